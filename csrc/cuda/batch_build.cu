@@ -1,0 +1,115 @@
+// Mini-batch construction on the device (W1 of SURVEY.md §8).
+// The host packs a batch record-major into ONE pinned staging buffer (keys of record 0,
+// record 1, ... plus per-record slot offsets) and issues ONE H2D copy; this kernel turns
+// it into the slot-major layout every sparse op consumes: keys[N] ordered by (slot, ins)
+// and lod[S*B+1].  No D2H round trip, no per-slot tensors.
+// Reference: MiniBatchGpuPack (6-9 H2D copies + sync, data_feed.cc:4896-4940) +
+// FillSlotValueOffsetPadBoxKernel (serial per-slot scan) + D2H of the offsets +
+// CopyForTensorPadBoxKernel (data_feed.cu:1208-1384, data_feed.cc:3400-3522).
+#include "common.cuh"
+#include <cooperative_groups.h>
+namespace cg = cooperative_groups;
+
+namespace {
+
+constexpr int BB_THREADS = 512;
+
+__device__ __forceinline__ int bag_len(const int32_t* ro, int S, int B, int g) {
+  const int s = g / B, b = g % B;
+  const int32_t* r = ro + (int64_t)b * (S + 1) + s;
+  return r[1] - r[0];
+}
+
+// block-wide exclusive scan of one int per thread; returns exclusive prefix, *total = block sum
+__device__ __forceinline__ int block_exscan(int v, int* total) {
+  __shared__ int warp_sums[BB_THREADS / 32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  int inc = v;
+  for (int o = 1; o < 32; o <<= 1) {
+    int t = __shfl_up_sync(0xffffffffu, inc, o);
+    if (lane >= o) inc += t;
+  }
+  if (lane == 31) warp_sums[w] = inc;
+  __syncthreads();
+  if (w == 0) {
+    int ws = lane < BB_THREADS / 32 ? warp_sums[lane] : 0;
+    int winc = ws;
+    for (int o = 1; o < 32; o <<= 1) {
+      int t = __shfl_up_sync(0xffffffffu, winc, o);
+      if (lane >= o) winc += t;
+    }
+    if (lane < BB_THREADS / 32) warp_sums[lane] = winc - ws;  // exclusive warp offsets
+    if (lane == BB_THREADS / 32 - 1) *total = winc;
+  }
+  __syncthreads();
+  int res = inc - v + warp_sums[w];
+  __syncthreads();
+  return res;
+}
+
+__global__ void __launch_bounds__(BB_THREADS)
+k_batch_build(const uint64_t* __restrict__ rec_keys, const int32_t* __restrict__ rec_off, int B, int S,
+              uint64_t* __restrict__ keys_out, int32_t* __restrict__ lod_out, int32_t* __restrict__ block_sums) {
+  cg::grid_group grid = cg::this_grid();
+  const int G = S * B;
+  const int per_block = (G + gridDim.x - 1) / gridDim.x;
+  const int g0 = blockIdx.x * per_block, g1 = min(G, g0 + per_block);
+  __shared__ int s_total;
+  __shared__ int s_carry;
+
+  // phase 1: per-block total length
+  int local = 0;
+  for (int g = g0 + threadIdx.x; g < g1; g += BB_THREADS) local += bag_len(rec_off, S, B, g);
+  int dummy = block_exscan(local, &s_total);
+  (void)dummy;
+  if (threadIdx.x == 0) block_sums[blockIdx.x] = s_total;
+  grid.sync();
+
+  // phase 2: every block derives its base from the (few) block sums
+  int base = 0;
+  for (int i = threadIdx.x; i < (int)blockIdx.x; i += BB_THREADS) base += block_sums[i];
+  int unused = block_exscan(base, &s_total);
+  (void)unused;
+  if (threadIdx.x == 0) s_carry = s_total;
+  __syncthreads();
+
+  // phase 3: chunked scan inside the block -> lod, then scatter keys
+  for (int c0 = g0; c0 < g1; c0 += BB_THREADS) {
+    const int g = c0 + threadIdx.x;
+    const int len = g < g1 ? bag_len(rec_off, S, B, g) : 0;
+    const int ex = block_exscan(len, &s_total);
+    const int start = s_carry + ex;
+    if (g < g1) {
+      lod_out[g] = start;
+      const int s = g / B, b = g % B;
+      const int32_t src = rec_off[(int64_t)b * (S + 1) + s];
+      for (int j = 0; j < len; ++j) keys_out[start + j] = rec_keys[src + j];
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) s_carry += s_total;
+    __syncthreads();
+  }
+  if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) lod_out[G] = s_carry;
+}
+
+}  // namespace
+
+extern "C" {
+
+// d_rec_off: [B, S+1] global offsets into d_rec_keys (record-major CSR).
+// d_scratch: >= 1024 int32 of scratch for the cross-block scan.
+int pbx_batch_build(const uint64_t* d_rec_keys, const int32_t* d_rec_off, int B, int S, uint64_t* d_keys_out,
+                    int32_t* d_lod_out, int32_t* d_scratch, cudaStream_t st) {
+  if (B <= 0 || S <= 0) return 0;
+  int G = S * B;
+  int blocks = (G + BB_THREADS * 4 - 1) / (BB_THREADS * 4);
+  int sms = pbx_num_sms();
+  if (blocks > sms) blocks = sms;
+  if (blocks < 1) blocks = 1;
+  void* args[] = {(void*)&d_rec_keys, (void*)&d_rec_off, (void*)&B, (void*)&S, (void*)&d_keys_out,
+                  (void*)&d_lod_out, (void*)&d_scratch};
+  PBX_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_batch_build, dim3(blocks), dim3(BB_THREADS), args, 0, st));
+  return 0;
+}
+
+}  // extern "C"

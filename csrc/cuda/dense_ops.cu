@@ -1,0 +1,400 @@
+// Dense-side helper kernels of the CTR step (all plain HBM-bound SIMT — no GEMM shape):
+//   cast+transpose feeding the tcgen05 GEMMs, column sums (bias grads), fused flat Adam
+//   (+ bf16 weight refresh), FM interaction head, sigmoid+log-loss, CVM, data_norm,
+//   AUC bucketing, replica-cache gather.
+// Reference kernels replaced: cvm_op.cu:29-75, data_norm_op.cu:39-110, metrics.cc:115-136
+// (host bucketing under a mutex), box_wrapper.cu:1210-1224, phi adam / log_loss /
+// sigmoid / scale kernels.
+#include "common.cuh"
+
+namespace {
+
+// fp32 [M, K] (ld) -> bf16 [M, ldo] (+ optional bf16 transposed [K, ldt]); 32x32 smem tiles
+__global__ void k_cast_transpose(const float* __restrict__ x, int ld, int M, int K, __nv_bfloat16* __restrict__ out,
+                                 int ldo, __nv_bfloat16* __restrict__ out_t, int ldt) {
+  __shared__ float tile[32][33];
+  const int m0 = blockIdx.y * 32, k0 = blockIdx.x * 32;
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    int m = m0 + r, k = k0 + threadIdx.x;
+    float v = (m < M && k < K) ? x[(int64_t)m * ld + k] : 0.f;
+    tile[r][threadIdx.x] = v;
+    if (out && m < M && k < K) out[(int64_t)m * ldo + k] = __float2bfloat16(v);
+  }
+  if (!out_t) return;
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    int k = k0 + r, m = m0 + threadIdx.x;
+    if (k < K && m < M) out_t[(int64_t)k * ldt + m] = __float2bfloat16(tile[threadIdx.x][r]);
+  }
+}
+
+// out[n] += sum_m x[m, n]   (x bf16 [M, ld])
+__global__ void k_colsum_bf16(const __nv_bfloat16* __restrict__ x, int ld, int M, int N, float* __restrict__ out) {
+  const int n = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int rlane = threadIdx.x >> 5;      // 8 row lanes
+  const int rows_per_block = (M + gridDim.y - 1) / gridDim.y;
+  const int mbeg = blockIdx.y * rows_per_block, mend = min(M, mbeg + rows_per_block);
+  float acc = 0.f;
+  if (n < N)
+    for (int m = mbeg + rlane; m < mend; m += 8) acc += __bfloat162float(x[(int64_t)m * ld + n]);
+  __shared__ float red[8][33];
+  red[rlane][threadIdx.x & 31] = acc;
+  __syncthreads();
+  if (rlane == 0 && n < N) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += red[i][threadIdx.x & 31];
+    atomicAdd(out + n, s);
+  }
+}
+
+// flat Adam over every dense parameter at once (reference: one adam op per param).
+// step_dev[0] holds the step count t (float), advanced by the kernel's first thread.
+__global__ void k_adam_flat(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
+                            float* __restrict__ v, int64_t n, float lr, float b1, float b2, float eps,
+                            float weight_decay, float grad_scale, const float* __restrict__ step_dev,
+                            int zero_grad) {
+  const float t = step_dev[0] + 1.f;
+  const float c1 = 1.f - powf(b1, t), c2 = 1.f - powf(b2, t);
+  const float step_size = lr * sqrtf(c2) / c1;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    float gi = g[i] * grad_scale;
+    float pi = p[i];
+    if (weight_decay != 0.f) gi += weight_decay * pi;
+    float mi = b1 * m[i] + (1.f - b1) * gi;
+    float vi = b2 * v[i] + (1.f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    p[i] = pi - step_size * mi / (sqrtf(vi) + eps * sqrtf(c2));
+    if (zero_grad) g[i] = 0.f;
+  }
+}
+__global__ void k_step_inc(float* step_dev) { step_dev[0] += 1.f; }
+
+__global__ void k_sgd_flat(float* __restrict__ p, float* __restrict__ g, int64_t n, float lr, float grad_scale,
+                           int zero_grad) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    p[i] -= lr * grad_scale * g[i];
+    if (zero_grad) g[i] = 0.f;
+  }
+}
+
+// sigmoid + log-loss (mean) forward with the gradient produced in the same pass.
+//   pred = sigmoid(logit); loss += -(y log p + (1-y) log(1-p)) / B; dlogit = (p - y) * gscale
+__global__ void k_sigmoid_logloss(const float* __restrict__ logit, const float* __restrict__ label, int B,
+                                  float* __restrict__ pred, float* __restrict__ loss_sum,
+                                  float* __restrict__ dlogit, float gscale) {
+  float local = 0.f;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < B; i += gridDim.x * blockDim.x) {
+    float z = logit[i], y = label[i];
+    float p = 1.f / (1.f + __expf(-z));
+    if (pred) pred[i] = p;
+    // stable: max(z,0) - z*y + log(1+exp(-|z|))
+    local += fmaxf(z, 0.f) - z * y + log1pf(__expf(-fabsf(z)));
+    if (dlogit) dlogit[i] = (p - y) * gscale;
+  }
+  for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+  if ((threadIdx.x & 31) == 0 && loss_sum) atomicAdd(loss_sum, local / (float)B);
+}
+
+// DeepFM first/second-order head on pooled slot embeddings.
+//   x: [B, ldx], slot s occupies columns [s*E, (s+1)*E); column `wcol` is the first-order
+//   weight, columns [vcol, vcol+D) the factor vector.
+//   fm[b] = sum_s w_s + 0.5 * sum_d ((sum_s v_sd)^2 - sum_s v_sd^2)
+__global__ void k_fm_fwd(const float* __restrict__ x, int ldx, int B, int S, int E, int wcol, int vcol, int D,
+                         float* __restrict__ fm) {
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  for (int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < B; b += warps) {
+    const float* row = x + (int64_t)b * ldx;
+    float acc = 0.f;
+    for (int d = lane; d < D; d += 32) {
+      float sv = 0.f, sq = 0.f;
+      for (int s = 0; s < S; ++s) {
+        float v = row[s * E + vcol + d];
+        sv += v;
+        sq += v * v;
+      }
+      acc += 0.5f * (sv * sv - sq);
+    }
+    for (int s = lane; s < S; s += 32) acc += row[s * E + wcol];
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) fm[b] = acc;
+  }
+}
+// dx[b, s*E + wcol] += g[b];  dx[b, s*E+vcol+d] += g[b] * (sum_s' v_s'd - v_sd)
+__global__ void k_fm_bwd(const float* __restrict__ x, int ldx, const float* __restrict__ g, int B, int S, int E,
+                         int wcol, int vcol, int D, float* __restrict__ dx, int lddx, int accumulate) {
+  const int warps = (gridDim.x * blockDim.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  for (int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < B; b += warps) {
+    const float* row = x + (int64_t)b * ldx;
+    float* drow = dx + (int64_t)b * lddx;
+    const float gb = g[b];
+    for (int d = lane; d < D; d += 32) {
+      float sv = 0.f;
+      for (int s = 0; s < S; ++s) sv += row[s * E + vcol + d];
+      for (int s = 0; s < S; ++s) {
+        float gv = gb * (sv - row[s * E + vcol + d]);
+        float* o = drow + s * E + vcol + d;
+        *o = accumulate ? *o + gv : gv;
+      }
+    }
+    for (int s = lane; s < S; s += 32) {
+      float* o = drow + s * E + wcol;
+      *o = accumulate ? *o + gb : gb;
+    }
+  }
+}
+
+// standalone CVM transform (cvm_op.cu:29-75): use_cvm: y = [log(x0+1), log(x1+1)-log(x0+1), x2..]
+// else y = x[2:]
+__global__ void k_cvm_fwd(const float* __restrict__ x, int64_t rows, int W, int use_cvm, float* __restrict__ y) {
+  const int Wo = use_cvm ? W : W - 2;
+  const int64_t total = rows * Wo;
+  for (int64_t it = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; it < total;
+       it += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(it % Wo);
+    const int64_t r = it / Wo;
+    const float* xr = x + r * W;
+    float v;
+    if (use_cvm) v = c == 0 ? logf(xr[0] + 1.f) : (c == 1 ? logf(xr[1] + 1.f) - logf(xr[0] + 1.f) : xr[c]);
+    else v = xr[c + 2];
+    y[it] = v;
+  }
+}
+// dx = [cvm0, cvm1, dy...]  (cvm_op.cu:50-75)
+__global__ void k_cvm_bwd(const float* __restrict__ dy, const float* __restrict__ cvm, int64_t rows, int W,
+                          int use_cvm, float* __restrict__ dx) {
+  const int Wo = use_cvm ? W : W - 2;
+  const int64_t total = rows * W;
+  for (int64_t it = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; it < total;
+       it += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(it % W);
+    const int64_t r = it / W;
+    dx[it] = c < 2 ? cvm[r * 2 + c] : dy[r * Wo + (use_cvm ? c : c - 2)];
+  }
+}
+
+// data_norm forward: y = (x - sum/size) * sqrt(size/sqsum)   (data_norm_op.cu:39-60)
+__global__ void k_data_norm_fwd(const float* __restrict__ x, int64_t rows, int C, const float* __restrict__ bsize,
+                                const float* __restrict__ bsum, const float* __restrict__ bsq,
+                                float* __restrict__ y, float* __restrict__ means, float* __restrict__ scales) {
+  const int64_t total = rows * C;
+  for (int64_t it = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; it < total;
+       it += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(it % C);
+    const float mean = bsum[c] / bsize[c];
+    const float scale = sqrtf(bsize[c] / bsq[c]);
+    y[it] = (x[it] - mean) * scale;
+    if (it < C) { means[c] = mean; scales[c] = scale; }
+  }
+}
+// backward: dx = dy * scale; per-column batch statistics for the three summaries
+//   d_size = 1, d_sum = mean(x), d_sqsum = mean((x-mean)^2) + eps   (GPU kernel, data_norm_op.cu:67-88)
+__global__ void k_data_norm_bwd(const float* __restrict__ x, const float* __restrict__ dy, int64_t rows, int C,
+                                const float* __restrict__ means, const float* __restrict__ scales, float eps,
+                                float* __restrict__ dx, float* __restrict__ d_size, float* __restrict__ d_sum,
+                                float* __restrict__ d_sq) {
+  // grid.x over column tiles of 32, grid.y over row chunks
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int rlane = threadIdx.x >> 5;
+  const int64_t rpb = (rows + gridDim.y - 1) / gridDim.y;
+  const int64_t r0 = blockIdx.y * rpb, r1 = min(rows, r0 + rpb);
+  float s = 0.f, q = 0.f;
+  if (c < C) {
+    const float mean = means[c], scale = scales[c];
+    for (int64_t r = r0 + rlane; r < r1; r += 8) {
+      float xv = x[r * C + c];
+      if (dx) dx[r * C + c] = dy[r * C + c] * scale;
+      s += xv;
+      q += (xv - mean) * (xv - mean);
+    }
+  }
+  __shared__ float rs[8][33], rq[8][33];
+  rs[rlane][threadIdx.x & 31] = s;
+  rq[rlane][threadIdx.x & 31] = q;
+  __syncthreads();
+  if (rlane == 0 && c < C) {
+    float ts = 0.f, tq = 0.f;
+    for (int i = 0; i < 8; ++i) { ts += rs[i][threadIdx.x & 31]; tq += rq[i][threadIdx.x & 31]; }
+    const float inv = 1.f / (float)rows;
+    atomicAdd(d_sum + c, ts * inv);
+    atomicAdd(d_sq + c, tq * inv + (blockIdx.y == 0 ? eps : 0.f));
+    if (blockIdx.y == 0) d_size[c] = 1.f;
+  }
+}
+
+// AUC bucketing on device (W9): table[0][bucket] += (1 - label), table[1][bucket] += label,
+// plus running sums {abs_err, sq_err, pred, label, count} in fp64.
+// Reference does a D2H copy and buckets on the CPU under a mutex (metrics.cc:115-136).
+__global__ void k_auc_bucket(const float* __restrict__ pred, const float* __restrict__ label,
+                             const float* __restrict__ mask, int64_t n, int nbuckets,
+                             double* __restrict__ table /* [2, nbuckets] */, double* __restrict__ sums /* [5] */) {
+  double l_abs = 0, l_sq = 0, l_pred = 0, l_lab = 0, l_cnt = 0;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    if (mask && mask[i] == 0.f) continue;
+    float p = pred[i], y = label[i];
+    p = fminf(fmaxf(p, 0.f), 1.f);
+    int bkt = min((int)(p * (float)nbuckets), nbuckets - 1);
+    atomicAdd(table + bkt, (double)(1.f - y));
+    atomicAdd(table + nbuckets + bkt, (double)y);
+    l_abs += fabs((double)p - y);
+    l_sq += ((double)p - y) * ((double)p - y);
+    l_pred += p;
+    l_lab += y;
+    l_cnt += 1;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    l_abs += __shfl_xor_sync(0xffffffffu, l_abs, o);
+    l_sq += __shfl_xor_sync(0xffffffffu, l_sq, o);
+    l_pred += __shfl_xor_sync(0xffffffffu, l_pred, o);
+    l_lab += __shfl_xor_sync(0xffffffffu, l_lab, o);
+    l_cnt += __shfl_xor_sync(0xffffffffu, l_cnt, o);
+  }
+  if ((threadIdx.x & 31) == 0 && l_cnt > 0) {
+    atomicAdd(sums + 0, l_abs);
+    atomicAdd(sums + 1, l_sq);
+    atomicAdd(sums + 2, l_pred);
+    atomicAdd(sums + 3, l_lab);
+    atomicAdd(sums + 4, l_cnt);
+  }
+}
+
+// replica cache gather (box_wrapper.cu:1210-1224): out[i, :] = table[idx[i], :]
+__global__ void k_row_gather(const float* __restrict__ table, const int64_t* __restrict__ idx, int64_t n, int dim,
+                             float* __restrict__ out) {
+  const int64_t total = n * dim;
+  for (int64_t it = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; it < total;
+       it += (int64_t)gridDim.x * blockDim.x)
+    out[it] = table[idx[it / dim] * dim + it % dim];
+}
+
+// L2 flush helper for benches: writes a buffer larger than L2
+__global__ void k_fill_u32(uint32_t* p, int64_t n, uint32_t v) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    p[i] = v;
+}
+
+}  // namespace
+
+extern "C" {
+
+int pbx_cast_transpose(const float* x, int ld, int M, int K, void* out_bf16, int ldo, void* out_t, int ldt,
+                       cudaStream_t st) {
+  if (M <= 0 || K <= 0) return 0;
+  dim3 grid((K + 31) / 32, (M + 31) / 32);
+  k_cast_transpose<<<grid, dim3(32, 8), 0, st>>>(x, ld, M, K, (__nv_bfloat16*)out_bf16, ldo, (__nv_bfloat16*)out_t,
+                                                 ldt);
+  PBX_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pbx_colsum_bf16(const void* x, int ld, int M, int N, float* out, cudaStream_t st) {
+  if (M <= 0 || N <= 0) return 0;
+  int gy = (M + 255) / 256;
+  if (gy > 64) gy = 64;
+  k_colsum_bf16<<<dim3((N + 31) / 32, gy), 256, 0, st>>>((const __nv_bfloat16*)x, ld, M, N, out);
+  PBX_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pbx_adam_flat(float* p, float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
+                  float weight_decay, float grad_scale, float* step_dev, int zero_grad, cudaStream_t st) {
+  if (n <= 0) return 0;
+  k_adam_flat<<<pbx_grid_for(n, 256, 8), 256, 0, st>>>(p, g, m, v, n, lr, b1, b2, eps, weight_decay, grad_scale,
+                                                       step_dev, zero_grad);
+  k_step_inc<<<1, 1, 0, st>>>(step_dev);
+  PBX_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pbx_sgd_flat(float* p, float* g, int64_t n, float lr, float grad_scale, int zero_grad, cudaStream_t st) {
+  if (n <= 0) return 0;
+  k_sgd_flat<<<pbx_grid_for(n, 256, 8), 256, 0, st>>>(p, g, n, lr, grad_scale, zero_grad);
+  PBX_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pbx_sigmoid_logloss(const float* logit, const float* label, int B, float* pred, float* loss_sum, float* dlogit,
+                        float gscale, cudaStream_t st) {
+  if (B <= 0) return 0;
+  k_sigmoid_logloss<<<pbx_grid_for(B, 256, 1), 256, 0, st>>>(logit, label, B, pred, loss_sum, dlogit, gscale);
+  PBX_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pbx_fm_fwd(const float* x, int ldx, int B, int S, int E, int wcol, int vcol, int D, float* fm, cudaStream_t st) {
+  if (B <= 0) return 0;
+  k_fm_fwd<<<pbx_grid_for((long long)B * 32, 256, 8), 256, 0, st>>>(x, ldx, B, S, E, wcol, vcol, D, fm);
+  PBX_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pbx_fm_bwd(const float* x, int ldx, const float* g, int B, int S, int E, int wcol, int vcol, int D, float* dx,
+               int lddx, int accumulate, cudaStream_t st) {
+  if (B <= 0) return 0;
+  k_fm_bwd<<<pbx_grid_for((long long)B * 32, 256, 8), 256, 0, st>>>(x, ldx, g, B, S, E, wcol, vcol, D, dx, lddx,
+                                                                     accumulate);
+  PBX_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pbx_cvm_fwd(const float* x, int64_t rows, int W, int use_cvm, float* y, cudaStream_t st) {
+  int64_t total = rows * (use_cvm ? W : W - 2);
+  if (total <= 0) return 0;
+  k_cvm_fwd<<<pbx_grid_for(total, 256, 8), 256, 0, st>>>(x, rows, W, use_cvm, y);
+  PBX_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pbx_cvm_bwd(const float* dy, const float* cvm, int64_t rows, int W, int use_cvm, float* dx, cudaStream_t st) {
+  if (rows * W <= 0) return 0;
+  k_cvm_bwd<<<pbx_grid_for(rows * W, 256, 8), 256, 0, st>>>(dy, cvm, rows, W, use_cvm, dx);
+  PBX_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pbx_data_norm_fwd(const float* x, int64_t rows, int C, const float* bsize, const float* bsum, const float* bsq,
+                      float* y, float* means, float* scales, cudaStream_t st) {
+  if (rows * C <= 0) return 0;
+  k_data_norm_fwd<<<pbx_grid_for(rows * C, 256, 8), 256, 0, st>>>(x, rows, C, bsize, bsum, bsq, y, means, scales);
+  PBX_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// d_size/d_sum/d_sq must be zeroed by the caller (they are accumulated with atomics)
+int pbx_data_norm_bwd(const float* x, const float* dy, int64_t rows, int C, const float* means, const float* scales,
+                      float eps, float* dx, float* d_size, float* d_sum, float* d_sq, cudaStream_t st) {
+  if (rows * C <= 0) return 0;
+  int gy = (int)((rows + 255) / 256);
+  if (gy > 64) gy = 64;
+  if (gy < 1) gy = 1;
+  k_data_norm_bwd<<<dim3((C + 31) / 32, gy), 256, 0, st>>>(x, dy, rows, C, means, scales, eps, dx, d_size, d_sum,
+                                                           d_sq);
+  PBX_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pbx_auc_bucket(const float* pred, const float* label, const float* mask, int64_t n, int nbuckets, double* table,
+                   double* sums, cudaStream_t st) {
+  if (n <= 0) return 0;
+  k_auc_bucket<<<pbx_grid_for(n, 256, 2), 256, 0, st>>>(pred, label, mask, n, nbuckets, table, sums);
+  PBX_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pbx_row_gather(const float* table, const int64_t* idx, int64_t n, int dim, float* out, cudaStream_t st) {
+  if (n * dim <= 0) return 0;
+  k_row_gather<<<pbx_grid_for(n * dim, 256, 8), 256, 0, st>>>(table, idx, n, dim, out);
+  PBX_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+int pbx_l2_flush(void* buf, int64_t bytes, cudaStream_t st) {
+  k_fill_u32<<<pbx_grid_for(bytes / 4, 256, 8), 256, 0, st>>>((uint32_t*)buf, bytes / 4, 0u);
+  PBX_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

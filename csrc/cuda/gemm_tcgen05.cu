@@ -1,0 +1,421 @@
+// Dense-tower GEMM on the 5th-gen tensor cores (W7 of SURVEY.md §8):
+//
+//     C[M,N] = epilogue( alpha * A[M,K] . B[N,K]^T )        A, B bf16, K-contiguous
+//
+// * operands staged by TMA (cp.async.bulk.tensor, 128B swizzle) through a 4-stage
+//   mbarrier ring, multiplied by tcgen05.mma (cta_group::1, M=128, N=BN, K=16) issued
+//   by one elected thread, accumulated in TMEM, read back with tcgen05.ld;
+// * warp roles: warp0 = TMA producer, warp1 = TMEM owner + MMA issuer, warps2-5 =
+//   epilogue (one TMEM lane quadrant each);
+// * fused epilogue: + bias[N], ReLU, * (mask > 0) (ReLU backward), bf16 row-major
+//   store, bf16 *transposed* store (feeds the next wgrad without a transpose pass),
+//   fp32 store, or fp32 atomic accumulate (split-K wgrad).
+//
+// All three GEMMs of a dense layer (fprop, dgrad, wgrad) are this one "TN" kernel:
+// transposed bf16 copies of activations / weights are produced by the epilogues.
+// Replaces the reference's cuBLAS calls (mul/fc phi kernels; scaled_fc_op.cu:214;
+// batch_fc_op.cu:243) — there is no tensor-core code in the reference.
+#include "common.cuh"
+#include <cuda.h>
+#include <cudaTypedefs.h>
+
+namespace {
+
+constexpr int BM = 128;
+constexpr int BK = 64;  // 64 bf16 = 128 bytes = one swizzle row
+constexpr int STAGES = 4;
+constexpr int GEMM_THREADS = 192;  // 6 warps
+
+struct GemmEpilogue {
+  const float* bias;          // [N] or null
+  const __nv_bfloat16* mask;  // [M, ld_mask] or null: out *= (mask > 0)
+  __nv_bfloat16* out_bf16;    // [M, ld_out] or null
+  __nv_bfloat16* out_t;       // [N, ld_t] or null  (transposed copy)
+  float* out_f32;             // [M, ld_f32] or null
+  int ld_mask, ld_out, ld_t, ld_f32;
+  int relu;
+  int accumulate;             // atomicAdd into out_f32 (split-K)
+  float alpha;
+};
+
+// ---------------- PTX wrappers ----------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t addr = smem_u32(bar);
+  uint32_t done = 0;
+  // bounded: a mis-programmed pipeline must trap, not hang the GPU
+  for (uint32_t spin = 0; spin < (1u << 28); ++spin) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(addr), "r"(parity)
+        : "memory");
+    if (done) return;
+  }
+  __trap();
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(smem_dst)), "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_slot, uint32_t cols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_slot)),
+               "r"(cols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem]
+__device__ __forceinline__ void umma_bf16(uint32_t tmem_d, uint64_t desc_a, uint64_t desc_b, uint32_t idesc,
+                                          uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(desc_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+        "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+        "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+        "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major, 128B-swizzled smem tile descriptor (cute::UMMA::SmemDescriptor, sm_100):
+//   [0,14) start>>4 | [16,30) LBO>>4 (unused for swizzled K-major) | [32,46) SBO>>4 = 1024B
+//   | [46,48) version = 1 | [61,64) layout = 2 (SWIZZLE_128B)
+__device__ __forceinline__ uint64_t make_smem_desc(const void* smem_tile) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_u32(smem_tile) & 0x3FFFF) >> 4);
+  d |= (uint64_t)(1024 >> 4) << 32;
+  d |= (uint64_t)1 << 46;
+  d |= (uint64_t)2 << 61;
+  return d;
+}
+// instruction descriptor (cute::UMMA::InstrDescriptor): c=F32 [4,6)=1, a=BF16 [7,10)=1,
+// b=BF16 [10,13)=1, a/b K-major, N>>3 at [17,23), M>>4 at [24,29)
+__host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
+  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
+}
+
+template <int BN>
+struct SmemLayout {
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int TOTAL = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+k_gemm_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, int M, int N,
+               int K, int kb_per_split, GemmEpilogue ep) {
+  extern __shared__ uint8_t smem_raw[];
+  using L = SmemLayout<BN>;
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * L::STAGE_BYTES);
+  uint64_t* empty_bar = full_bar + STAGES;
+  uint64_t* tmem_full_bar = empty_bar + STAGES;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * BM;
+  const int n0 = blockIdx.y * BN;
+  const int num_kb_total = (K + BK - 1) / BK;
+  const int kb_begin = blockIdx.z * kb_per_split;
+  const int kb_end = min(kb_begin + kb_per_split, num_kb_total);
+  const int num_kb = kb_end - kb_begin;
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    for (int s = 0; s < STAGES; ++s) {
+      mbar_init(full_bar + s, 1);
+      mbar_init(empty_bar + s, 1);
+    }
+    mbar_init(tmem_full_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, BN);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (num_kb > 0) {
+    if (warp == 0) {
+      // ===== TMA producer =====
+      if (lane == 0) {
+        for (int i = 0; i < num_kb; ++i) {
+          const int s = i % STAGES;
+          const uint32_t ph = (uint32_t)(i / STAGES) & 1u;
+          mbar_wait(empty_bar + s, ph ^ 1u);
+          uint8_t* sa = smem + s * L::STAGE_BYTES;
+          uint8_t* sb = sa + L::A_BYTES;
+          mbar_expect_tx(full_bar + s, (uint32_t)L::STAGE_BYTES);
+          const int kc = (kb_begin + i) * BK;
+          tma_load_2d(sa, &map_a, full_bar + s, kc, m0);
+          tma_load_2d(sb, &map_b, full_bar + s, kc, n0);
+        }
+      }
+    } else if (warp == 1) {
+      // ===== MMA issuer =====
+      if (lane == 0) {
+        constexpr uint32_t idesc = make_idesc(BM, BN);
+        for (int i = 0; i < num_kb; ++i) {
+          const int s = i % STAGES;
+          const uint32_t ph = (uint32_t)(i / STAGES) & 1u;
+          mbar_wait(full_bar + s, ph);
+          tc_fence_after();
+          uint8_t* sa = smem + s * L::STAGE_BYTES;
+          uint8_t* sb = sa + L::A_BYTES;
+          const uint64_t da = make_smem_desc(sa);
+          const uint64_t db = make_smem_desc(sb);
+#pragma unroll
+          for (int k = 0; k < BK / 16; ++k) {
+            // advance 16 bf16 = 32 bytes along K inside the swizzle atom: +2 in the (>>4) address field
+            umma_bf16(tmem_base, da + (uint64_t)(2 * k), db + (uint64_t)(2 * k), idesc, (i | k) ? 1u : 0u);
+          }
+          umma_commit(empty_bar + s);  // frees the smem stage when these MMAs retire
+        }
+        umma_commit(tmem_full_bar);    // accumulator complete
+      }
+      __syncwarp();
+    } else {
+      // ===== epilogue: warps 2..5, TMEM lane quadrant = warp % 4 =====
+      const int q = warp & 3;
+      const int row = m0 + q * 32 + lane;
+      mbar_wait(tmem_full_bar, 0);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
+        if (n0 + c0 >= N) continue;
+        float v[32];
+#pragma unroll
+        for (int j = 0; j < 32; ++j) {
+          float x = __uint_as_float(r[j]) * ep.alpha;
+          const int n = n0 + c0 + j;
+          if (ep.bias && n < N) x += __ldg(ep.bias + n);
+          if (ep.relu) x = fmaxf(x, 0.f);
+          v[j] = x;
+        }
+        if (ep.mask && row < M) {
+          const __nv_bfloat16* mrow = ep.mask + (int64_t)row * ep.ld_mask + n0 + c0;
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (n0 + c0 + j < N && !(__bfloat162float(mrow[j]) > 0.f)) v[j] = 0.f;
+        }
+        if (row < M) {
+          if (ep.out_bf16) {
+            __nv_bfloat16* o = ep.out_bf16 + (int64_t)row * ep.ld_out + n0 + c0;
+            if (n0 + c0 + 32 <= N && (ep.ld_out & 7) == 0) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 8) {
+                __nv_bfloat162 p0 = __floats2bfloat162_rn(v[j], v[j + 1]);
+                __nv_bfloat162 p1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
+                __nv_bfloat162 p2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]);
+                __nv_bfloat162 p3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
+                uint4 pk;
+                pk.x = *reinterpret_cast<uint32_t*>(&p0);
+                pk.y = *reinterpret_cast<uint32_t*>(&p1);
+                pk.z = *reinterpret_cast<uint32_t*>(&p2);
+                pk.w = *reinterpret_cast<uint32_t*>(&p3);
+                *reinterpret_cast<uint4*>(o + j) = pk;
+              }
+            } else {
+              for (int j = 0; j < 32; ++j)
+                if (n0 + c0 + j < N) o[j] = __float2bfloat16(v[j]);
+            }
+          }
+          if (ep.out_f32) {
+            float* o = ep.out_f32 + (int64_t)row * ep.ld_f32 + n0 + c0;
+            if (ep.accumulate) {
+              for (int j = 0; j < 32; ++j)
+                if (n0 + c0 + j < N) atomicAdd(o + j, v[j]);
+            } else if (n0 + c0 + 32 <= N && (ep.ld_f32 & 3) == 0) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4)
+                *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            } else {
+              for (int j = 0; j < 32; ++j)
+                if (n0 + c0 + j < N) o[j] = v[j];
+            }
+          }
+          if (ep.out_t) {
+            // lanes are consecutive rows -> consecutive addresses in the transposed copy
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (n0 + c0 + j < N) ep.out_t[(int64_t)(n0 + c0 + j) * ep.ld_t + row] = __float2bfloat16(v[j]);
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, BN);
+}
+
+// --------- plain SIMT kernel with the same contract: numerics cross-check / fallback ---------
+__global__ void k_gemm_simt(const __nv_bfloat16* __restrict__ A, int lda, const __nv_bfloat16* __restrict__ B,
+                            int ldb, int M, int N, int K, GemmEpilogue ep) {
+  __shared__ float sa[16][17], sb[16][17];
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const int row = blockIdx.y * 16 + ty, col = blockIdx.x * 16 + tx;
+  float acc = 0.f;
+  for (int k0 = 0; k0 < K; k0 += 16) {
+    sa[ty][tx] = (row < M && k0 + tx < K) ? __bfloat162float(A[(int64_t)row * lda + k0 + tx]) : 0.f;
+    const int brow = blockIdx.x * 16 + ty;
+    sb[ty][tx] = (brow < N && k0 + tx < K) ? __bfloat162float(B[(int64_t)brow * ldb + k0 + tx]) : 0.f;
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 16; ++k) acc += sa[ty][k] * sb[tx][k];
+    __syncthreads();
+  }
+  if (row >= M || col >= N) return;
+  float x = acc * ep.alpha;
+  if (ep.bias) x += ep.bias[col];
+  if (ep.relu) x = fmaxf(x, 0.f);
+  if (ep.mask && !(__bfloat162float(ep.mask[(int64_t)row * ep.ld_mask + col]) > 0.f)) x = 0.f;
+  if (ep.out_bf16) ep.out_bf16[(int64_t)row * ep.ld_out + col] = __float2bfloat16(x);
+  if (ep.out_t) ep.out_t[(int64_t)col * ep.ld_t + row] = __float2bfloat16(x);
+  if (ep.out_f32) {
+    if (ep.accumulate) atomicAdd(ep.out_f32 + (int64_t)row * ep.ld_f32 + col, x);
+    else ep.out_f32[(int64_t)row * ep.ld_f32 + col] = x;
+  }
+}
+
+PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = (PFN_cuTensorMapEncodeTiled_v12000)p;
+  }
+  return fn;
+}
+
+int make_map(CUtensorMap* map, const void* base, int rows, int cols, int ld, int box_rows) {
+  auto fn = get_encode_fn();
+  PBX_REQUIRE(fn != nullptr, "cuTensorMapEncodeTiled entry point unavailable");
+  cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t gstride[1] = {(cuuint64_t)ld * 2};
+  cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  PBX_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d): base %p rows %d cols %d ld %d", (int)r, base,
+              rows, cols, ld);
+  return 0;
+}
+
+template <int BN>
+int launch_tc(const __nv_bfloat16* A, int lda, const __nv_bfloat16* B, int ldb, int M, int N, int K, int splitk,
+              const GemmEpilogue& ep, cudaStream_t st) {
+  CUtensorMap ma, mb;
+  int rc = make_map(&ma, A, M, K, lda, BM);
+  if (rc) return rc;
+  rc = make_map(&mb, B, N, K, ldb, BN);
+  if (rc) return rc;
+  const int num_kb = (K + BK - 1) / BK;
+  if (splitk < 1) splitk = 1;
+  if (splitk > num_kb) splitk = num_kb;
+  const int kb_per = (num_kb + splitk - 1) / splitk;
+  splitk = (num_kb + kb_per - 1) / kb_per;
+  static bool attr_set = false;
+  if (!attr_set) {
+    PBX_CUDA_CHECK(cudaFuncSetAttribute(k_gemm_tcgen05<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        SmemLayout<BN>::TOTAL));
+    attr_set = true;
+  }
+  dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, splitk);
+  k_gemm_tcgen05<BN><<<grid, GEMM_THREADS, SmemLayout<BN>::TOTAL, st>>>(ma, mb, M, N, K, kb_per, ep);
+  PBX_CUDA_CHECK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+// impl: 0 = tcgen05 (default), 1 = SIMT cross-check.  block_n in {32, 64, 128, 256} (0 = auto).
+// Requirements for the tcgen05 path: A/B 16-byte aligned, lda/ldb multiples of 8 elements.
+int pbx_gemm_bf16_tn(const void* A, int lda, const void* B, int ldb, int M, int N, int K, const float* bias,
+                     const void* mask, int ld_mask, void* out_bf16, int ld_out, void* out_t, int ld_t,
+                     float* out_f32, int ld_f32, int relu, int accumulate, float alpha, int splitk, int block_n,
+                     int impl, cudaStream_t st) {
+  if (M <= 0 || N <= 0) return 0;
+  PBX_REQUIRE(K > 0, "gemm: K must be positive");
+  GemmEpilogue ep;
+  ep.bias = bias;
+  ep.mask = (const __nv_bfloat16*)mask;
+  ep.out_bf16 = (__nv_bfloat16*)out_bf16;
+  ep.out_t = (__nv_bfloat16*)out_t;
+  ep.out_f32 = out_f32;
+  ep.ld_mask = ld_mask; ep.ld_out = ld_out; ep.ld_t = ld_t; ep.ld_f32 = ld_f32;
+  ep.relu = relu;
+  ep.accumulate = accumulate;
+  ep.alpha = alpha;
+  if (splitk > 1) PBX_REQUIRE(accumulate && out_f32 && !out_bf16 && !out_t && !relu && !bias && !mask,
+                              "gemm: split-K needs a pure fp32 accumulate epilogue");
+  if (impl == 1) {
+    dim3 grid((N + 15) / 16, (M + 15) / 16);
+    k_gemm_simt<<<grid, dim3(16, 16), 0, st>>>((const __nv_bfloat16*)A, lda, (const __nv_bfloat16*)B, ldb, M, N, K,
+                                               ep);
+    PBX_CUDA_CHECK(cudaGetLastError());
+    return 0;
+  }
+  PBX_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0 && (lda & 7) == 0 && (ldb & 7) == 0,
+              "gemm: tcgen05 path needs 16B-aligned operands and leading dims that are multiples of 8");
+  if (block_n == 0) {
+    // enough CTAs to cover the 148 SMs when the problem allows it
+    long long tiles128 = (long long)((M + BM - 1) / BM) * ((N + 127) / 128) * (splitk > 0 ? splitk : 1);
+    block_n = (N <= 32) ? 32 : (N <= 64 || tiles128 < 96) ? 64 : 128;
+  }
+  const __nv_bfloat16* a = (const __nv_bfloat16*)A;
+  const __nv_bfloat16* b = (const __nv_bfloat16*)B;
+  switch (block_n) {
+    case 32: return launch_tc<32>(a, lda, b, ldb, M, N, K, splitk, ep, st);
+    case 64: return launch_tc<64>(a, lda, b, ldb, M, N, K, splitk, ep, st);
+    case 128: return launch_tc<128>(a, lda, b, ldb, M, N, K, splitk, ep, st);
+    case 256: return launch_tc<256>(a, lda, b, ldb, M, N, K, splitk, ep, st);
+    default: PBX_REQUIRE(false, "gemm: unsupported block_n %d", block_n);
+  }
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,599 @@
+// Sharded sparse pull / push as ONE persistent cooperative kernel each (W2 / W3 of
+// SURVEY.md §8).  The all-to-all is done from inside the kernel with plain stores
+// into peer HBM over NVLink/NVSwitch (CUDA-IPC-mapped symmetric buffers); ranks meet
+// at flag barriers in peer memory.  No NCCL, no host round trip, no sort.
+//
+//   pull : dedup (batch-local hash) -> bucket by owner -> remote-store keys into the
+//          owner's mailbox -> barrier -> owner probes its shard and remote-stores the
+//          value rows straight into the requester's value buffer -> barrier.
+//   push : merge gradients by unique key (fp32 atomics into a local buffer, fused
+//          with the seqpool/CVM backward) -> remote-store merged records into the
+//          owner's mailbox -> barrier -> owner applies the fused sparse optimizer.
+//
+// Replaces the reference's host-orchestrated sequence: cub sort + per-peer
+// cudaMemcpyAsync + search/update kernels + >= 8 stream syncs
+// (heter_ps/heter_comm_inl.h:1117-1171, :1477-1622, :1646-1825; box_wrapper_impl.h:25-234,
+// :373-522; box_wrapper.cu:324-512).
+//
+// Testing on fewer GPUs than ranks: with EMU=true one launch runs all ranks as slices
+// of one cooperative grid on one GPU ("virtual ranks"); the cross-rank barrier then is
+// the grid barrier.  The per-rank code is identical.
+#include "sparse_a2a.cuh"
+#include <cooperative_groups.h>
+#include <vector>
+namespace cg = cooperative_groups;
+
+#define PBX_A2A_THREADS 512
+
+struct PbxPullArgs {
+  const uint64_t* keys;
+  int64_t n;
+  uint32_t* restore;  // [n] out: unique-value row of every occurrence
+};
+struct PbxPullArgsN { PbxPullArgs a[PBX_MAX_RANKS]; };
+
+struct PbxPushArgs {
+  const uint32_t* restore;  // [n] from the pull of the same batch
+  int64_t n;
+  // mode 0: gradients come from pooled output grads (fused seqpool/CVM backward)
+  const float* dout;        // [B, S*Eo]
+  const float* cvm;         // [B, cvm_offset]  (show, click labels)
+  const int32_t* lod;       // [S*B + 1] bag offsets, slot-major
+  int B, S, Eo, cvm_offset, dim_off;
+  // mode 1: explicit per-occurrence gradients [n, hidden] + slot of every occurrence
+  const float* gkeys;
+  const int32_t* key2slot;
+  int hidden;
+  int mode;
+  float grad_scale;         // -batch_size (box_wrapper.cu:404-410)
+};
+struct PbxPushArgsN { PbxPushArgs a[PBX_MAX_RANKS]; };
+
+namespace {
+
+template <bool EMU>
+__device__ __forceinline__ void xbarrier(cg::grid_group& grid, const PbxSparseDev& c, uint64_t target,
+                                         bool leader_block) {
+  __threadfence_system();
+  grid.sync();
+  if (!EMU && c.nranks > 1) {
+    if (leader_block && threadIdx.x < c.nranks) {
+      int p = threadIdx.x;
+      __threadfence_system();
+      pbx_st_release_sys(c.flags[p] + c.rank, target);
+      uint64_t t0 = pbx_globaltimer();
+      while (pbx_ld_acquire_sys(c.flags[c.rank] + p) < target) {
+        if (pbx_globaltimer() - t0 > 20000000000ull) {  // 20 s: a peer died; fail loudly, do not hang
+          atomicExch(c.status, 2);
+          break;
+        }
+      }
+    }
+    grid.sync();
+  }
+}
+
+template <bool EMU>
+__global__ void __launch_bounds__(PBX_A2A_THREADS, 1)
+k_sparse_pull(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPullArgsN args) {
+  cg::grid_group grid = cg::this_grid();
+  const int bpr = gridDim.x / nvr;         // blocks per (virtual) rank
+  const int vr = blockIdx.x / bpr;
+  const int lb = blockIdx.x % bpr;
+  const PbxSparseDev& c = ctxs[vr];
+  const PbxPullArgs a = args.a[vr];
+  const int R = c.nranks;
+  const uint32_t cap = c.cap;
+  const int tid = threadIdx.x;
+  const uint64_t e0 = *c.epoch;
+
+  __shared__ uint32_t s_cnt[PBX_MAX_RANKS];
+  __shared__ uint32_t s_base[PBX_MAX_RANKS];
+
+  // ---- P0: reset per-batch counters (dedup table was cleaned by the previous pull)
+  if (lb == 0 && tid < R) c.send_cnt[tid] = 0;
+  grid.sync();
+
+  // ---- P1: dedup + claim a mailbox slot per unique key + ship the key to its owner
+  {
+    const uint32_t mask = c.dd_cap - 1;
+    const int64_t chunk = (int64_t)bpr * PBX_A2A_THREADS;
+    const int64_t nround = (a.n + chunk - 1) / chunk;
+    for (int64_t r = 0; r < nround; ++r) {
+      int64_t i = r * chunk + (int64_t)lb * PBX_A2A_THREADS + tid;
+      if (tid < R) s_cnt[tid] = 0;
+      __syncthreads();
+      bool is_rep = false;
+      uint32_t pos = 0, lrank = 0;
+      int owner = 0;
+      uint64_t key = 0;
+      if (i < a.n) {
+        key = a.keys[i];
+        uint64_t h = pbx_mix64(key);
+        pos = (uint32_t)h & mask;
+        while (true) {
+          unsigned long long prev = atomicCAS(reinterpret_cast<unsigned long long*>(c.dd_keys + pos),
+                                              (unsigned long long)PBX_EMPTY_KEY, (unsigned long long)key);
+          if (prev == PBX_EMPTY_KEY) { is_rep = true; break; }
+          if (prev == key) break;
+          pos = (pos + 1) & mask;
+        }
+        a.restore[i] = pos;
+        if (is_rep) {
+          owner = pbx_owner_of(key, R);
+          lrank = atomicAdd(&s_cnt[owner], 1u);
+        }
+      }
+      __syncthreads();
+      if (tid < R) s_base[tid] = s_cnt[tid] ? atomicAdd(c.send_cnt + tid, s_cnt[tid]) : 0u;
+      __syncthreads();
+      if (is_rep) {
+        uint32_t slot = s_base[owner] + lrank;
+        if (slot < cap) {
+          c.dd_uid[pos] = (uint32_t)owner * cap + slot;
+          c.mail_keys[owner][(uint64_t)c.rank * cap + slot] = key;  // remote store (NVLink)
+        } else {
+          c.dd_uid[pos] = (uint32_t)owner * cap;  // keep indices in range; flagged below
+          atomicExch(c.status, 1);
+        }
+      }
+      __syncthreads();
+    }
+  }
+  grid.sync();
+
+  // ---- P2: occurrence -> unique row, publish counts, clean the dedup table
+  {
+    const int64_t stride = (int64_t)bpr * PBX_A2A_THREADS;
+    for (int64_t i = (int64_t)lb * PBX_A2A_THREADS + tid; i < a.n; i += stride)
+      a.restore[i] = c.dd_uid[a.restore[i]];
+    if (lb == 0 && tid < R) {
+      uint32_t n_send = min(c.send_cnt[tid], cap);
+      c.send_cnt[tid] = n_send;
+      c.mail_cnt[tid][c.rank] = n_send;  // remote store
+    }
+  }
+  grid.sync();  // all reads of dd_uid done before dd_keys is recycled
+  {
+    const int64_t stride = (int64_t)bpr * PBX_A2A_THREADS;
+    for (int64_t i = (int64_t)lb * PBX_A2A_THREADS + tid; i < (int64_t)c.dd_cap; i += stride)
+      c.dd_keys[i] = PBX_EMPTY_KEY;
+  }
+  xbarrier<EMU>(grid, c, e0 + 1, lb == 0);
+
+  // ---- P3: owner side — probe the local shard, return rows into the requester's buffer
+  {
+    const int lane = tid & 31;
+    const int warp = lb * (PBX_A2A_THREADS / 32) + (tid >> 5);
+    const int nwarps = bpr * (PBX_A2A_THREADS / 32);
+    const int PS = c.pull_stride;
+    const int chunks = PS >> 2;
+    const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int s = 0; s < R; ++s) {
+      const uint32_t cnt = min(__ldcg(c.mail_cnt[c.rank] + s), cap);
+      if (lb == 0 && tid == 0) c.serve_cnt[s] = cnt;
+      const uint64_t* mk = c.mail_keys[c.rank] + (uint64_t)s * cap;
+      uint32_t* mrow = c.mail_row + (uint64_t)s * cap;
+      float* dst = c.pull_vals[s] + (uint64_t)c.rank * cap * PS;  // requester s, my region
+      for (uint32_t j0 = (uint32_t)warp * 32u; j0 < cnt; j0 += (uint32_t)nwarps * 32u) {
+        uint32_t j = j0 + lane;
+        uint32_t row = PBX_NO_ROW;
+        if (j < cnt) {
+          uint64_t key = __ldcg(mk + j);
+          if (key != 0) row = pbx_dev_find(c.table, key);
+          mrow[j] = row;
+        }
+        const uint32_t nvalid = min(32u, cnt - j0);
+        const uint32_t items = nvalid * (uint32_t)chunks;
+        for (uint32_t it0 = 0; it0 < items; it0 += 32) {
+          uint32_t it = it0 + lane;
+          uint32_t kk = min(it / (uint32_t)chunks, 31u);
+          uint32_t ch = it % (uint32_t)chunks;
+          uint32_t r = __shfl_sync(0xffffffffu, row, kk);
+          if (it < items) {
+            float4 v = zero4;
+            if (r != PBX_NO_ROW)
+              v = *reinterpret_cast<const float4*>(c.table.vals + (uint64_t)r * c.table.L.stride + ch * 4);
+            *reinterpret_cast<float4*>(dst + (uint64_t)(j0 + kk) * PS + ch * 4) = v;  // remote store
+          }
+        }
+      }
+    }
+  }
+  xbarrier<EMU>(grid, c, e0 + 2, lb == 0);
+  if (lb == 0 && tid == 0) *c.epoch = e0 + 2;
+}
+
+template <bool EMU>
+__global__ void __launch_bounds__(PBX_A2A_THREADS, 1)
+k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args) {
+  cg::grid_group grid = cg::this_grid();
+  const int bpr = gridDim.x / nvr;
+  const int vr = blockIdx.x / bpr;
+  const int lb = blockIdx.x % bpr;
+  const PbxSparseDev& c = ctxs[vr];
+  const PbxPushArgs a = args.a[vr];
+  const int R = c.nranks;
+  const uint32_t cap = c.cap;
+  const int tid = threadIdx.x;
+  const int PD = c.push_stride;
+  const int pchunks = PD >> 2;
+  const int64_t gtid = (int64_t)lb * PBX_A2A_THREADS + tid;
+  const int64_t gstride = (int64_t)bpr * PBX_A2A_THREADS;
+  const uint64_t e0 = *c.epoch;
+
+  // ---- Q0: zero the merge rows in use
+  for (int o = 0; o < R; ++o) {
+    const int64_t items = (int64_t)c.send_cnt[o] * pchunks;
+    float4* base = reinterpret_cast<float4*>(c.push_acc + (uint64_t)o * cap * PD);
+    for (int64_t it = gtid; it < items; it += gstride) base[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  grid.sync();
+
+  // ---- Q1: merge by unique key (fused with the seqpool/CVM backward in mode 0)
+  if (a.mode == 0) {
+    const int hidden = 3 + c.table.L.embedx_dim;
+    const int64_t items = (int64_t)a.S * a.B * hidden;
+    for (int64_t it = gtid; it < items; it += gstride) {
+      const int col = (int)(it % hidden);
+      const int64_t g = it / hidden;  // bag = slot * B + ins
+      const int s = (int)(g / a.B);
+      const int b = (int)(g % a.B);
+      const int32_t k0 = a.lod[g], k1 = a.lod[g + 1];
+      if (k0 >= k1) continue;
+      float v;
+      if (col < a.cvm_offset) v = a.cvm[(int64_t)b * a.cvm_offset + col];
+      else v = a.grad_scale * a.dout[(int64_t)b * a.S * a.Eo + (int64_t)s * a.Eo + (col - a.dim_off)];
+      for (int32_t k = k0; k < k1; ++k) {
+        float* rec = c.push_acc + (uint64_t)a.restore[k] * PD;
+        atomicAdd(rec + col + 1, v);
+        if (col == 0) rec[0] = (float)s;
+      }
+    }
+  } else {
+    const int hidden = a.hidden;
+    const int64_t items = a.n * hidden;
+    for (int64_t it = gtid; it < items; it += gstride) {
+      const int col = (int)(it % hidden);
+      const int64_t i = it / hidden;
+      float v = a.gkeys[it];
+      if (col >= a.cvm_offset) v *= a.grad_scale;
+      float* rec = c.push_acc + (uint64_t)a.restore[i] * PD;
+      atomicAdd(rec + col + 1, v);
+      if (col == 0) rec[0] = (float)a.key2slot[i];
+    }
+  }
+  grid.sync();
+
+  // ---- Q2: ship merged records to their owners
+  for (int o = 0; o < R; ++o) {
+    const int64_t items = (int64_t)c.send_cnt[o] * pchunks;
+    const float4* src = reinterpret_cast<const float4*>(c.push_acc + (uint64_t)o * cap * PD);
+    float4* dst = reinterpret_cast<float4*>(c.push_mail[o] + (uint64_t)c.rank * cap * PD);  // remote
+    for (int64_t it = gtid; it < items; it += gstride) dst[it] = src[it];
+  }
+  xbarrier<EMU>(grid, c, e0 + 1, lb == 0);
+
+  // ---- Q3: owner applies the optimizer; one requester at a time so that a key pushed by
+  // several ranks is updated once per rank without a race (reference applies per-GPU
+  // pushes one after another under the table write lock, heter_comm_inl.h:1779-1804).
+  for (int s = 0; s < R; ++s) {
+    const uint32_t cnt = c.serve_cnt[s];
+    if (!c.table.test_mode) {
+      const float* pm = c.push_mail[c.rank] + (uint64_t)s * cap * PD;
+      const uint32_t* mrow = c.mail_row + (uint64_t)s * cap;
+      for (int64_t j = gtid; j < (int64_t)cnt; j += gstride) {
+        uint32_t row = mrow[j];
+        if (row == PBX_NO_ROW) continue;
+        // the key comes from the table itself: a faster peer may already be overwriting
+        // this rank's key mailbox with the next batch
+        pbx_apply_push(c.table, row, c.table.keys[row], pm + j * PD);
+      }
+    }
+    if (s + 1 < R) grid.sync();
+  }
+  if (lb == 0 && tid == 0) *c.epoch = e0 + 1;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------
+// Host object
+// ---------------------------------------------------------------------------
+struct PbxSparseCtx {
+  PbxSparseDev h;          // host copy of the device context
+  PbxSparseDev* d;         // device copy
+  bool dirty;
+  int device;
+  void* symm_base;         // one allocation holding every symmetric buffer
+  size_t symm_bytes;
+  size_t off_flags, off_cnt, off_keys, off_vals, off_push;
+  void* peer_base[PBX_MAX_RANKS];
+  bool peer_opened[PBX_MAX_RANKS];
+  int64_t max_keys;
+  int grid_blocks;         // cooperative grid size (per real rank)
+  void* table;             // PbxTable*
+};
+
+static void pbx_ctx_bind_peer(PbxSparseCtx* c, int p, void* base) {
+  char* b = (char*)base;
+  c->peer_base[p] = base;
+  c->h.flags[p] = (uint64_t*)(b + c->off_flags);
+  c->h.mail_cnt[p] = (uint32_t*)(b + c->off_cnt);
+  c->h.mail_keys[p] = (uint64_t*)(b + c->off_keys);
+  c->h.pull_vals[p] = (float*)(b + c->off_vals);
+  c->h.push_mail[p] = (float*)(b + c->off_push);
+  c->dirty = true;
+}
+
+extern "C" {
+
+// Creates the per-rank engine: allocates the symmetric region and local scratch.
+//   max_keys : largest number of key occurrences in one batch on this rank
+//   cap      : mailbox capacity per (src,dst) pair (0 = choose: all of max_keys for 1 rank,
+//              else 2x the even share + slack)
+int pbx_sparse_create(void** out, void* table, int rank, int nranks, int64_t max_keys, int64_t cap) {
+  PBX_REQUIRE(nranks >= 1 && nranks <= PBX_MAX_RANKS, "nranks %d out of range (max %d)", nranks, PBX_MAX_RANKS);
+  PBX_REQUIRE(rank >= 0 && rank < nranks, "bad rank %d", rank);
+  PBX_REQUIRE(max_keys > 0, "max_keys must be positive");
+  PbxTable* t = (PbxTable*)table;
+  PbxSparseCtx* c = new PbxSparseCtx();
+  memset(c, 0, sizeof(*c));
+  cudaGetDevice(&c->device);
+  c->table = table;
+  c->max_keys = max_keys;
+  if (cap <= 0) cap = nranks == 1 ? max_keys : (2 * max_keys / nranks + 1024);
+  if (cap > max_keys) cap = max_keys;
+  PBX_REQUIRE((uint64_t)cap * nranks < 0xFFFFFFF0ull, "mailbox too large");
+  PbxSparseDev& h = c->h;
+  h.rank = rank;
+  h.nranks = nranks;
+  h.cap = (uint32_t)cap;
+  uint64_t dd = 1024;
+  while (dd < (uint64_t)max_keys * 2) dd <<= 1;
+  h.dd_cap = (uint32_t)dd;
+  h.pull_stride = t->view.L.pull_stride;
+  h.push_stride = t->view.L.push_stride;
+  h.table = t->view;
+  auto al = [](size_t x) { return (x + 255) / 256 * 256; };
+  size_t off = 0;
+  c->off_flags = off; off += al(64 * sizeof(uint64_t));
+  c->off_cnt = off;   off += al(64 * sizeof(uint32_t));
+  c->off_keys = off;  off += al((size_t)nranks * cap * sizeof(uint64_t));
+  c->off_vals = off;  off += al((size_t)nranks * cap * h.pull_stride * sizeof(float));
+  c->off_push = off;  off += al((size_t)nranks * cap * h.push_stride * sizeof(float));
+  c->symm_bytes = off;
+  PBX_CUDA_CHECK(cudaMalloc(&c->symm_base, c->symm_bytes));
+  PBX_CUDA_CHECK(cudaMemset(c->symm_base, 0, c->symm_bytes));
+  PBX_CUDA_CHECK(cudaMalloc(&h.dd_keys, dd * sizeof(uint64_t)));
+  PBX_CUDA_CHECK(cudaMemset(h.dd_keys, 0xFF, dd * sizeof(uint64_t)));
+  PBX_CUDA_CHECK(cudaMalloc(&h.dd_uid, dd * sizeof(uint32_t)));
+  PBX_CUDA_CHECK(cudaMalloc(&h.send_cnt, 64 * sizeof(uint32_t)));
+  PBX_CUDA_CHECK(cudaMalloc(&h.serve_cnt, 64 * sizeof(uint32_t)));
+  PBX_CUDA_CHECK(cudaMemset(h.send_cnt, 0, 64 * sizeof(uint32_t)));
+  PBX_CUDA_CHECK(cudaMemset(h.serve_cnt, 0, 64 * sizeof(uint32_t)));
+  PBX_CUDA_CHECK(cudaMalloc(&h.mail_row, (size_t)nranks * cap * sizeof(uint32_t)));
+  PBX_CUDA_CHECK(cudaMalloc(&h.push_acc, (size_t)nranks * cap * h.push_stride * sizeof(float)));
+  PBX_CUDA_CHECK(cudaMalloc(&h.epoch, 256));
+  PBX_CUDA_CHECK(cudaMemset(h.epoch, 0, 256));
+  h.status = (int*)(h.epoch + 8);
+  PBX_CUDA_CHECK(cudaMalloc(&c->d, sizeof(PbxSparseDev)));
+  pbx_ctx_bind_peer(c, rank, c->symm_base);
+  // cooperative grid: one CTA per SM
+  int bps = 0;
+  PBX_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_sparse_pull<false>, PBX_A2A_THREADS, 0));
+  PBX_REQUIRE(bps >= 1, "sparse pull kernel does not fit on an SM");
+  c->grid_blocks = pbx_num_sms();
+  PBX_CUDA_CHECK(cudaDeviceSynchronize());
+  *out = c;
+  return 0;
+}
+
+int pbx_sparse_destroy(void* hnd) {
+  PbxSparseCtx* c = (PbxSparseCtx*)hnd;
+  if (!c) return 0;
+  for (int p = 0; p < c->h.nranks; ++p)
+    if (c->peer_opened[p]) cudaIpcCloseMemHandle(c->peer_base[p]);
+  cudaFree(c->symm_base);
+  cudaFree(c->h.dd_keys);
+  cudaFree(c->h.dd_uid);
+  cudaFree(c->h.send_cnt);
+  cudaFree(c->h.serve_cnt);
+  cudaFree(c->h.mail_row);
+  cudaFree(c->h.push_acc);
+  cudaFree(c->h.epoch);
+  cudaFree(c->d);
+  delete c;
+  return 0;
+}
+
+// 64-byte CUDA IPC handle of this rank's symmetric region (exchange through the
+// torch.distributed store, then call pbx_sparse_connect on every rank).
+int pbx_sparse_ipc_handle(void* hnd, void* out64) {
+  PbxSparseCtx* c = (PbxSparseCtx*)hnd;
+  cudaIpcMemHandle_t mh;
+  PBX_CUDA_CHECK(cudaIpcGetMemHandle(&mh, c->symm_base));
+  memcpy(out64, &mh, sizeof(mh));
+  return 0;
+}
+
+int pbx_sparse_connect(void* hnd, const void* handles /* nranks * 64 bytes */) {
+  PbxSparseCtx* c = (PbxSparseCtx*)hnd;
+  for (int p = 0; p < c->h.nranks; ++p) {
+    if (p == c->h.rank) continue;
+    cudaIpcMemHandle_t mh;
+    memcpy(&mh, (const char*)handles + (size_t)p * sizeof(mh), sizeof(mh));
+    void* base = nullptr;
+    PBX_CUDA_CHECK(cudaIpcOpenMemHandle(&base, mh, cudaIpcMemLazyEnablePeerAccess));
+    c->peer_opened[p] = true;
+    pbx_ctx_bind_peer(c, p, base);
+  }
+  return 0;
+}
+
+// Same-process wiring (virtual ranks on one GPU, or several GPUs driven by one process).
+int pbx_sparse_connect_local(void* hnd, void* const* peers) {
+  PbxSparseCtx* c = (PbxSparseCtx*)hnd;
+  for (int p = 0; p < c->h.nranks; ++p) {
+    if (p == c->h.rank) continue;
+    PbxSparseCtx* o = (PbxSparseCtx*)peers[p];
+    PBX_REQUIRE(o->h.cap == c->h.cap && o->h.nranks == c->h.nranks, "peer context geometry differs");
+    pbx_ctx_bind_peer(c, p, o->symm_base);
+  }
+  return 0;
+}
+
+int pbx_sparse_geometry(void* hnd, int64_t* cap, int64_t* n_unique_rows, int* pull_stride, int* push_stride) {
+  PbxSparseCtx* c = (PbxSparseCtx*)hnd;
+  *cap = c->h.cap;
+  *n_unique_rows = (int64_t)c->h.cap * c->h.nranks;
+  *pull_stride = c->h.pull_stride;
+  *push_stride = c->h.push_stride;
+  return 0;
+}
+
+// Device address of this rank's unique-value buffer [nranks*cap, pull_stride]; rows are
+// addressed by the restore index written by pbx_sparse_pull.
+float* pbx_sparse_pull_values(void* hnd) {
+  PbxSparseCtx* c = (PbxSparseCtx*)hnd;
+  return c->h.pull_vals[c->h.rank];
+}
+
+static int pbx_ctx_sync_dev(PbxSparseCtx* c, cudaStream_t st) {
+  PbxTable* t = (PbxTable*)c->table;
+  if (memcmp(&c->h.table, &t->view, sizeof(PbxTableView)) != 0) {
+    c->h.table = t->view;
+    c->dirty = true;
+  }
+  if (c->dirty) {
+    PBX_CUDA_CHECK(cudaMemcpyAsync(c->d, &c->h, sizeof(PbxSparseDev), cudaMemcpyHostToDevice, st));
+    PBX_CUDA_CHECK(cudaStreamSynchronize(st));  // h is pageable: make the copy complete before h changes
+    c->dirty = false;
+  }
+  return 0;
+}
+
+int pbx_sparse_status(void* hnd, int* status, int reset, cudaStream_t st) {
+  PbxSparseCtx* c = (PbxSparseCtx*)hnd;
+  PBX_CUDA_CHECK(cudaMemcpyAsync(status, c->h.status, sizeof(int), cudaMemcpyDeviceToHost, st));
+  PBX_CUDA_CHECK(cudaStreamSynchronize(st));
+  if (reset && *status) PBX_CUDA_CHECK(cudaMemsetAsync(c->h.status, 0, sizeof(int), st));
+  return 0;
+}
+
+int pbx_sparse_pull(void* hnd, const uint64_t* d_keys, int64_t n, uint32_t* d_restore, cudaStream_t st) {
+  PbxSparseCtx* c = (PbxSparseCtx*)hnd;
+  PBX_REQUIRE(n <= c->max_keys, "batch has %lld keys, engine was sized for %lld", (long long)n,
+              (long long)c->max_keys);
+  int rc = pbx_ctx_sync_dev(c, st);
+  if (rc) return rc;
+  PbxPullArgsN args;
+  memset(&args, 0, sizeof(args));
+  args.a[0].keys = d_keys;
+  args.a[0].n = n;
+  args.a[0].restore = d_restore;
+  const PbxSparseDev* dctx = c->d;
+  int nvr = 1;
+  void* kargs[] = {(void*)&dctx, (void*)&nvr, (void*)&args};
+  PBX_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_sparse_pull<false>, dim3(c->grid_blocks),
+                                             dim3(PBX_A2A_THREADS), kargs, 0, st));
+  return 0;
+}
+
+static int pbx_fill_push_args(PbxPushArgs& a, const uint32_t* d_restore, int64_t n, const float* d_dout,
+                              const float* d_cvm, const int32_t* d_lod, int B, int S, int Eo, int cvm_offset,
+                              int dim_off, const float* d_gkeys, const int32_t* d_key2slot, int hidden, int mode,
+                              float grad_scale) {
+  a.restore = d_restore; a.n = n; a.dout = d_dout; a.cvm = d_cvm; a.lod = d_lod;
+  a.B = B; a.S = S; a.Eo = Eo; a.cvm_offset = cvm_offset; a.dim_off = dim_off;
+  a.gkeys = d_gkeys; a.key2slot = d_key2slot; a.hidden = hidden; a.mode = mode; a.grad_scale = grad_scale;
+  return 0;
+}
+
+// mode 0: d_dout [B, S*Eo] pooled-output grads, d_cvm [B, cvm_offset], d_lod [S*B+1]
+// mode 1: d_gkeys [n, hidden] per-occurrence grads, d_key2slot [n]
+int pbx_sparse_push(void* hnd, const uint32_t* d_restore, int64_t n, const float* d_dout, const float* d_cvm,
+                    const int32_t* d_lod, int B, int S, int Eo, int cvm_offset, int dim_off, const float* d_gkeys,
+                    const int32_t* d_key2slot, int hidden, int mode, float grad_scale, cudaStream_t st) {
+  PbxSparseCtx* c = (PbxSparseCtx*)hnd;
+  PBX_REQUIRE(c->h.table.L.embedx_dim <= 256, "embedx_dim > 256 not supported by the push kernel");
+  if (mode == 0)
+    PBX_REQUIRE(Eo + dim_off == 3 + c->h.table.L.embedx_dim, "pooled width %d + %d != hidden %d", Eo, dim_off,
+                3 + c->h.table.L.embedx_dim);
+  else
+    PBX_REQUIRE(hidden == 3 + c->h.table.L.embedx_dim, "grad width %d != hidden", hidden);
+  int rc = pbx_ctx_sync_dev(c, st);
+  if (rc) return rc;
+  PbxPushArgsN args;
+  memset(&args, 0, sizeof(args));
+  pbx_fill_push_args(args.a[0], d_restore, n, d_dout, d_cvm, d_lod, B, S, Eo, cvm_offset, dim_off, d_gkeys,
+                     d_key2slot, hidden, mode, grad_scale);
+  const PbxSparseDev* dctx = c->d;
+  int nvr = 1;
+  void* kargs[] = {(void*)&dctx, (void*)&nvr, (void*)&args};
+  PBX_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_sparse_push<false>, dim3(c->grid_blocks),
+                                             dim3(PBX_A2A_THREADS), kargs, 0, st));
+  return 0;
+}
+
+// ---- virtual-rank emulation: all ranks of a same-process group in ONE launch on one GPU
+int pbx_sparse_pull_emu(void* const* hnds, int nranks, const uint64_t* const* d_keys, const int64_t* n,
+                        uint32_t* const* d_restore, cudaStream_t st) {
+  PBX_REQUIRE(nranks >= 1 && nranks <= PBX_MAX_RANKS, "bad nranks");
+  std::vector<PbxSparseDev> hs(nranks);
+  PbxPullArgsN args;
+  memset(&args, 0, sizeof(args));
+  for (int r = 0; r < nranks; ++r) {
+    PbxSparseCtx* c = (PbxSparseCtx*)hnds[r];
+    PBX_REQUIRE(n[r] <= c->max_keys, "batch too large for rank %d", r);
+    c->h.table = ((PbxTable*)c->table)->view;
+    hs[r] = c->h;
+    args.a[r].keys = d_keys[r];
+    args.a[r].n = n[r];
+    args.a[r].restore = d_restore[r];
+  }
+  PbxSparseDev* d = nullptr;
+  PBX_CUDA_CHECK(cudaMalloc(&d, sizeof(PbxSparseDev) * nranks));
+  PBX_CUDA_CHECK(cudaMemcpy(d, hs.data(), sizeof(PbxSparseDev) * nranks, cudaMemcpyHostToDevice));
+  int bpr = pbx_num_sms() / nranks;
+  if (bpr < 1) bpr = 1;
+  const PbxSparseDev* dctx = d;
+  void* kargs[] = {(void*)&dctx, (void*)&nranks, (void*)&args};
+  cudaError_t e = cudaLaunchCooperativeKernel((void*)k_sparse_pull<true>, dim3(bpr * nranks), dim3(PBX_A2A_THREADS),
+                                              kargs, 0, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFree(d);
+  PBX_CUDA_CHECK(e);
+  return 0;
+}
+
+int pbx_sparse_push_emu(void* const* hnds, int nranks, const uint32_t* const* d_restore, const int64_t* n,
+                        const float* const* d_dout, const float* const* d_cvm, const int32_t* const* d_lod, int B,
+                        int S, int Eo, int cvm_offset, int dim_off, float grad_scale, cudaStream_t st) {
+  PBX_REQUIRE(nranks >= 1 && nranks <= PBX_MAX_RANKS, "bad nranks");
+  std::vector<PbxSparseDev> hs(nranks);
+  PbxPushArgsN args;
+  memset(&args, 0, sizeof(args));
+  for (int r = 0; r < nranks; ++r) {
+    PbxSparseCtx* c = (PbxSparseCtx*)hnds[r];
+    c->h.table = ((PbxTable*)c->table)->view;
+    hs[r] = c->h;
+    pbx_fill_push_args(args.a[r], d_restore[r], n[r], d_dout[r], d_cvm[r], d_lod[r], B, S, Eo, cvm_offset, dim_off,
+                       nullptr, nullptr, 0, 0, grad_scale);
+  }
+  PbxSparseDev* d = nullptr;
+  PBX_CUDA_CHECK(cudaMalloc(&d, sizeof(PbxSparseDev) * nranks));
+  PBX_CUDA_CHECK(cudaMemcpy(d, hs.data(), sizeof(PbxSparseDev) * nranks, cudaMemcpyHostToDevice));
+  int bpr = pbx_num_sms() / nranks;
+  if (bpr < 1) bpr = 1;
+  const PbxSparseDev* dctx = d;
+  void* kargs[] = {(void*)&dctx, (void*)&nranks, (void*)&args};
+  cudaError_t e = cudaLaunchCooperativeKernel((void*)k_sparse_push<true>, dim3(bpr * nranks), dim3(PBX_A2A_THREADS),
+                                              kargs, 0, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFree(d);
+  PBX_CUDA_CHECK(e);
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,252 @@
+// Symmetric (peer-mapped) device memory + the dense-gradient collective kernels that run
+// over it (W8 of SURVEY.md §8).  Every rank allocates the same-sized region, exchanges
+// CUDA IPC handles once, and from then on kernels read and write peer HBM directly.
+//
+//   allreduce : ONE cooperative kernel = barrier -> two-shot reduce (each rank sums its
+//               slice from all peers with 16-byte P2P loads, multiplies by `scale`, and
+//               stores the result into every peer's buffer) -> barrier.  The 1/nranks
+//               gradient scale — a separate `scale` op after c_allreduce_sum in the
+//               reference (transpiler/collective.py:240-315, boxps_worker.cc:1235-1239)
+//               — is fused into the reduction.
+//   reduce_scatter / all_gather : the two halves, for ZeRO-1 style sharding
+//               (boxps_worker.cc:1220-1233).
+//   broadcast : root's slice to everyone (c_broadcast in sharding mode).
+// NCCL remains available in parallel/ as the labelled baseline and for multi-node.
+#include "common.cuh"
+#include <cooperative_groups.h>
+#include <vector>
+namespace cg = cooperative_groups;
+
+struct PbxSymmDev {
+  int rank, nranks;
+  uint64_t* flags[PBX_MAX_RANKS];  // [64] per rank
+  float* data[PBX_MAX_RANKS];      // user region per rank
+  uint64_t* epoch;
+  int* status;
+};
+
+struct PbxSymm {
+  PbxSymmDev h;
+  PbxSymmDev* d;
+  bool dirty;
+  void* base;
+  size_t bytes, data_off;
+  void* peer_base[PBX_MAX_RANKS];
+  bool opened[PBX_MAX_RANKS];
+};
+
+namespace {
+
+template <bool EMU>
+__device__ __forceinline__ void symm_barrier(cg::grid_group& grid, const PbxSymmDev& c, uint64_t target,
+                                             bool leader_block) {
+  __threadfence_system();
+  grid.sync();
+  if (!EMU && c.nranks > 1) {
+    if (leader_block && threadIdx.x < c.nranks) {
+      int p = threadIdx.x;
+      __threadfence_system();
+      pbx_st_release_sys(c.flags[p] + c.rank, target);
+      uint64_t t0 = pbx_globaltimer();
+      while (pbx_ld_acquire_sys(c.flags[c.rank] + p) < target) {
+        if (pbx_globaltimer() - t0 > 20000000000ull) { atomicExch(c.status, 2); break; }
+      }
+    }
+    grid.sync();
+  }
+}
+
+__device__ __forceinline__ float4 ld_f4_cg(const float* p) { return __ldcg(reinterpret_cast<const float4*>(p)); }
+
+// op: 0 allreduce, 1 reduce_scatter (result only in own slice), 2 all_gather (own slice -> all),
+//     3 broadcast from `root`, 4 barrier only
+template <bool EMU>
+__global__ void __launch_bounds__(512, 1)
+k_symm_collective(const PbxSymmDev* __restrict__ ctxs, int nvr, int64_t off, int64_t n, float scale, int op,
+                  int root) {
+  cg::grid_group grid = cg::this_grid();
+  const int bpr = gridDim.x / nvr;
+  const int vr = blockIdx.x / bpr;
+  const int lb = blockIdx.x % bpr;
+  const PbxSymmDev& c = ctxs[vr];
+  const int R = c.nranks;
+  const uint64_t e0 = *c.epoch;
+  const int64_t gtid = (int64_t)lb * blockDim.x + threadIdx.x;
+  const int64_t gstride = (int64_t)bpr * blockDim.x;
+
+  symm_barrier<EMU>(grid, c, e0 + 1, lb == 0);  // everybody's input is in place
+
+  // slice r = [r*chunk, min(n, (r+1)*chunk)), chunk a multiple of 4 floats
+  const int64_t chunk = ((n + R - 1) / R + 3) / 4 * 4;
+  if (op == 0 || op == 1) {
+    const int64_t b = min(n, (int64_t)c.rank * chunk), e = min(n, b + chunk);
+    const int64_t nv = (e - b) / 4;
+    for (int64_t i = gtid; i < nv; i += gstride) {
+      const int64_t idx = off + b + i * 4;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int p = 0; p < PBX_MAX_RANKS; ++p) {
+        if (p < R) {
+          float4 v = ld_f4_cg(c.data[(c.rank + p) % R] + idx);
+          acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+      }
+      acc.x *= scale; acc.y *= scale; acc.z *= scale; acc.w *= scale;
+      if (op == 0) {
+#pragma unroll
+        for (int p = 0; p < PBX_MAX_RANKS; ++p)
+          if (p < R) *reinterpret_cast<float4*>(c.data[(c.rank + p) % R] + idx) = acc;
+      } else {
+        *reinterpret_cast<float4*>(c.data[c.rank] + idx) = acc;
+      }
+    }
+    // tail (n not a multiple of 4): last slice owner handles scalars
+    for (int64_t i = b + nv * 4 + gtid; i < e; i += gstride) {
+      float acc = 0.f;
+      for (int p = 0; p < R; ++p) acc += __ldcg(c.data[p] + off + i);
+      acc *= scale;
+      if (op == 0) for (int p = 0; p < R; ++p) c.data[p][off + i] = acc;
+      else c.data[c.rank][off + i] = acc;
+    }
+  } else if (op == 2) {
+    const int64_t b = min(n, (int64_t)c.rank * chunk), e = min(n, b + chunk);
+    for (int64_t i = b + gtid; i < e; i += gstride) {
+      float v = c.data[c.rank][off + i];
+      for (int p = 0; p < R; ++p)
+        if (p != c.rank) c.data[p][off + i] = v;
+    }
+  } else if (op == 3) {
+    if (c.rank == root)
+      for (int64_t i = gtid; i < n; i += gstride) {
+        float v = c.data[root][off + i];
+        for (int p = 0; p < R; ++p)
+          if (p != root) c.data[p][off + i] = v;
+      }
+  }
+  symm_barrier<EMU>(grid, c, e0 + 2, lb == 0);  // every peer's stores have landed
+  if (lb == 0 && threadIdx.x == 0) *c.epoch = e0 + 2;
+}
+
+void symm_bind(PbxSymm* s, int p, void* base) {
+  s->peer_base[p] = base;
+  s->h.flags[p] = (uint64_t*)base;
+  s->h.data[p] = (float*)((char*)base + s->data_off);
+  s->dirty = true;
+}
+
+}  // namespace
+
+extern "C" {
+
+int pbx_symm_create(void** out, int rank, int nranks, uint64_t bytes) {
+  PBX_REQUIRE(nranks >= 1 && nranks <= PBX_MAX_RANKS && rank >= 0 && rank < nranks, "bad rank/nranks");
+  PbxSymm* s = new PbxSymm();
+  memset(s, 0, sizeof(*s));
+  s->h.rank = rank;
+  s->h.nranks = nranks;
+  s->data_off = 1024;
+  s->bytes = s->data_off + (bytes + 255) / 256 * 256;
+  PBX_CUDA_CHECK(cudaMalloc(&s->base, s->bytes));
+  PBX_CUDA_CHECK(cudaMemset(s->base, 0, s->bytes));
+  PBX_CUDA_CHECK(cudaMalloc(&s->h.epoch, 256));
+  PBX_CUDA_CHECK(cudaMemset(s->h.epoch, 0, 256));
+  s->h.status = (int*)(s->h.epoch + 8);
+  PBX_CUDA_CHECK(cudaMalloc(&s->d, sizeof(PbxSymmDev)));
+  symm_bind(s, rank, s->base);
+  PBX_CUDA_CHECK(cudaDeviceSynchronize());
+  *out = s;
+  return 0;
+}
+
+int pbx_symm_destroy(void* h) {
+  PbxSymm* s = (PbxSymm*)h;
+  if (!s) return 0;
+  for (int p = 0; p < s->h.nranks; ++p)
+    if (s->opened[p]) cudaIpcCloseMemHandle(s->peer_base[p]);
+  cudaFree(s->base);
+  cudaFree(s->h.epoch);
+  cudaFree(s->d);
+  delete s;
+  return 0;
+}
+
+void* pbx_symm_ptr(void* h) { return ((PbxSymm*)h)->h.data[((PbxSymm*)h)->h.rank]; }
+
+int pbx_symm_ipc_handle(void* h, void* out64) {
+  cudaIpcMemHandle_t mh;
+  PBX_CUDA_CHECK(cudaIpcGetMemHandle(&mh, ((PbxSymm*)h)->base));
+  memcpy(out64, &mh, sizeof(mh));
+  return 0;
+}
+
+int pbx_symm_connect(void* h, const void* handles) {
+  PbxSymm* s = (PbxSymm*)h;
+  for (int p = 0; p < s->h.nranks; ++p) {
+    if (p == s->h.rank) continue;
+    cudaIpcMemHandle_t mh;
+    memcpy(&mh, (const char*)handles + (size_t)p * sizeof(mh), sizeof(mh));
+    void* base = nullptr;
+    PBX_CUDA_CHECK(cudaIpcOpenMemHandle(&base, mh, cudaIpcMemLazyEnablePeerAccess));
+    s->opened[p] = true;
+    symm_bind(s, p, base);
+  }
+  return 0;
+}
+
+int pbx_symm_connect_local(void* h, void* const* peers) {
+  PbxSymm* s = (PbxSymm*)h;
+  for (int p = 0; p < s->h.nranks; ++p)
+    if (p != s->h.rank) symm_bind(s, p, ((PbxSymm*)peers[p])->base);
+  return 0;
+}
+
+int pbx_symm_status(void* h, int* status, cudaStream_t st) {
+  PbxSymm* s = (PbxSymm*)h;
+  PBX_CUDA_CHECK(cudaMemcpyAsync(status, s->h.status, sizeof(int), cudaMemcpyDeviceToHost, st));
+  PBX_CUDA_CHECK(cudaStreamSynchronize(st));
+  return 0;
+}
+
+// op: 0 allreduce(sum)*scale, 1 reduce_scatter, 2 all_gather, 3 broadcast(root), 4 barrier.
+// `off`/`n` in fp32 elements relative to pbx_symm_ptr(); off must be a multiple of 4.
+int pbx_symm_collective(void* h, int64_t off, int64_t n, float scale, int op, int root, int max_blocks,
+                        cudaStream_t st) {
+  PbxSymm* s = (PbxSymm*)h;
+  PBX_REQUIRE((off & 3) == 0, "collective offset must be a multiple of 4 elements");
+  PBX_REQUIRE((uint64_t)(off + n) * 4 <= s->bytes - s->data_off, "collective range exceeds the symmetric region");
+  if (s->dirty) {
+    PBX_CUDA_CHECK(cudaMemcpyAsync(s->d, &s->h, sizeof(PbxSymmDev), cudaMemcpyHostToDevice, st));
+    PBX_CUDA_CHECK(cudaStreamSynchronize(st));
+    s->dirty = false;
+  }
+  int blocks = (int)((n / 4 / s->h.nranks + 511) / 512);
+  int cap = max_blocks > 0 ? max_blocks : 64;  // leave SMs to the compute stream when overlapped
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  const PbxSymmDev* d = s->d;
+  int nvr = 1;
+  void* args[] = {(void*)&d, (void*)&nvr, (void*)&off, (void*)&n, (void*)&scale, (void*)&op, (void*)&root};
+  PBX_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_symm_collective<false>, dim3(blocks), dim3(512), args, 0, st));
+  return 0;
+}
+
+// all virtual ranks in one launch on one GPU (tests)
+int pbx_symm_collective_emu(void* const* hs, int nranks, int64_t off, int64_t n, float scale, int op, int root,
+                            cudaStream_t st) {
+  std::vector<PbxSymmDev> hv(nranks);
+  for (int r = 0; r < nranks; ++r) hv[r] = ((PbxSymm*)hs[r])->h;
+  PbxSymmDev* d = nullptr;
+  PBX_CUDA_CHECK(cudaMalloc(&d, sizeof(PbxSymmDev) * nranks));
+  PBX_CUDA_CHECK(cudaMemcpy(d, hv.data(), sizeof(PbxSymmDev) * nranks, cudaMemcpyHostToDevice));
+  int bpr = 8;
+  const PbxSymmDev* dc = d;
+  void* args[] = {(void*)&dc, (void*)&nranks, (void*)&off, (void*)&n, (void*)&scale, (void*)&op, (void*)&root};
+  cudaError_t e =
+      cudaLaunchCooperativeKernel((void*)k_symm_collective<true>, dim3(bpr * nranks), dim3(512), args, 0, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFree(d);
+  PBX_CUDA_CHECK(e);
+  return 0;
+}
+
+}  // extern "C"

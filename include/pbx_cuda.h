@@ -1,0 +1,139 @@
+/* paddlebox_b200 — C ABI of the sm_100a kernel library (libpbx_cuda.so).
+ *
+ * Every function returns 0 on success; on failure it returns a CUDA error code (> 0) or
+ * -1 and pbx_last_error() describes the problem.  `stream` arguments are cudaStream_t
+ * handles (pass torch.cuda.current_stream().cuda_stream).  Pointers prefixed d_ are
+ * device pointers.  Reference citations are relative to the PaddleBox tree.
+ */
+#ifndef PBX_CUDA_H_
+#define PBX_CUDA_H_
+#include <stdint.h>
+#include "pbx_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* pbx_stream_t;
+
+const char* pbx_last_error(void);
+
+/* ---- sparse table shard (csrc/cuda/table.cu) --------------------------------
+ * reference: heter_ps/hashtable.h, hashtable_kernel.cu:34-337, optimizer.cuh.h,
+ * ctr_dymf_accessor.cc:68-142 (shrink). */
+int pbx_table_create(void** out, uint64_t capacity, int embedx_dim, int optimizer,
+                     const PbxSparseOptConfig* cfg, uint64_t seed);
+int pbx_table_destroy(void* table);
+int pbx_table_layout(void* table, PbxRowLayout* out);
+int pbx_table_set_config(void* table, const PbxSparseOptConfig* cfg);
+int pbx_table_set_test_mode(void* table, int on);
+int pbx_table_clear(void* table, pbx_stream_t stream);
+int pbx_table_insert(void* table, const uint64_t* d_keys, int64_t n, const float* d_rows, pbx_stream_t stream);
+int pbx_table_fill_synthetic(void* table, uint64_t n_total, uint64_t key_seed, int rank, int nranks,
+                             int create_mf, pbx_stream_t stream);
+int pbx_table_count(void* table, int64_t* out, pbx_stream_t stream);
+int pbx_table_dump(void* table, uint64_t* d_keys_out, float* d_rows_out, int64_t max_n, int mode,
+                   int clear_dirty, int64_t* n_out, pbx_stream_t stream);
+int pbx_table_lookup(void* table, const uint64_t* d_keys, int64_t n, float* d_out, int out_stride,
+                     uint32_t* d_rows_out, pbx_stream_t stream);
+int pbx_table_update(void* table, const uint64_t* d_keys, const float* d_push, int push_stride, int64_t n,
+                     pbx_stream_t stream);
+int pbx_table_shrink(void* table, float decay, float delete_threshold, float delete_after_unseen_days,
+                     int64_t* kept, pbx_stream_t stream);
+
+/* ---- sharded sparse pull / push over NVLink peer memory (csrc/cuda/sparse_a2a.cu) ----
+ * reference: HeterComm::pull_sparse / push_sparse (heter_ps/heter_comm_inl.h:1477-1825),
+ * BoxWrapper::PullSparseCaseGPU / PushSparseGradCaseGPU (fleet/box_wrapper_impl.h:25-522),
+ * dedup contract heter_comm_inl.h:2231-2343. */
+int pbx_sparse_create(void** out, void* table, int rank, int nranks, int64_t max_keys, int64_t cap);
+int pbx_sparse_destroy(void* ctx);
+int pbx_sparse_ipc_handle(void* ctx, void* out64);
+int pbx_sparse_connect(void* ctx, const void* handles);
+int pbx_sparse_connect_local(void* ctx, void* const* peers);
+int pbx_sparse_geometry(void* ctx, int64_t* cap, int64_t* n_unique_rows, int* pull_stride, int* push_stride);
+float* pbx_sparse_pull_values(void* ctx);
+int pbx_sparse_status(void* ctx, int* status, int reset, pbx_stream_t stream);
+int pbx_sparse_pull(void* ctx, const uint64_t* d_keys, int64_t n, uint32_t* d_restore, pbx_stream_t stream);
+int pbx_sparse_push(void* ctx, const uint32_t* d_restore, int64_t n, const float* d_dout, const float* d_cvm,
+                    const int32_t* d_lod, int B, int S, int Eo, int cvm_offset, int dim_off, const float* d_gkeys,
+                    const int32_t* d_key2slot, int hidden, int mode, float grad_scale, pbx_stream_t stream);
+int pbx_sparse_pull_emu(void* const* ctxs, int nranks, const uint64_t* const* d_keys, const int64_t* n,
+                        uint32_t* const* d_restore, pbx_stream_t stream);
+int pbx_sparse_push_emu(void* const* ctxs, int nranks, const uint32_t* const* d_restore, const int64_t* n,
+                        const float* const* d_dout, const float* const* d_cvm, const int32_t* const* d_lod, int B,
+                        int S, int Eo, int cvm_offset, int dim_off, float grad_scale, pbx_stream_t stream);
+
+/* ---- fused_seqpool_cvm family (csrc/cuda/seqpool.cu) ------------------------
+ * reference: operators/fused/fused_seqpool_cvm_op.cu:34-1349 and the
+ * _with_conv/_with_credit/_with_diff_thres/_tradew variants. */
+int pbx_seqpool_cvm_fwd(const PbxSeqpoolParams* p, const float* d_x, const uint32_t* d_restore,
+                        const int32_t* d_lod, float* d_out, pbx_stream_t stream);
+int pbx_seqpool_cvm_bwd(const PbxSeqpoolParams* p, const float* d_dout, const float* d_cvm,
+                        const int32_t* d_lod, float* d_dx, int dx_stride, pbx_stream_t stream);
+int pbx_pull_scatter(const float* d_vals, int vstride, const uint32_t* d_restore, int64_t n, int hidden, int skip,
+                     float scale_embedx, float* d_out, pbx_stream_t stream);
+int pbx_key2slot(const int32_t* d_lod, int B, int S, int64_t n, int32_t* d_out, pbx_stream_t stream);
+
+/* ---- tcgen05 / TMA GEMM (csrc/cuda/gemm_tcgen05.cu) -------------------------
+ * C = epilogue(alpha * A[M,K] . B[N,K]^T); A, B bf16 K-contiguous.
+ * reference call sites: scaled_fc_op.cu:214, batch_fc_op.cu:243, rank_attention_op.cu:110,
+ * phi mul/matmul/fc kernels (all cuBLAS). */
+int pbx_gemm_bf16_tn(const void* A, int lda, const void* B, int ldb, int M, int N, int K, const float* bias,
+                     const void* mask, int ld_mask, void* out_bf16, int ld_out, void* out_t, int ld_t,
+                     float* out_f32, int ld_f32, int relu, int accumulate, float alpha, int splitk, int block_n,
+                     int impl, pbx_stream_t stream);
+
+/* ---- dense helpers (csrc/cuda/dense_ops.cu) --------------------------------- */
+int pbx_cast_transpose(const float* x, int ld, int M, int K, void* out_bf16, int ldo, void* out_t, int ldt,
+                       pbx_stream_t stream);
+int pbx_colsum_bf16(const void* x, int ld, int M, int N, float* out, pbx_stream_t stream);
+int pbx_adam_flat(float* p, float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
+                  float weight_decay, float grad_scale, float* step_dev, int zero_grad, pbx_stream_t stream);
+int pbx_sgd_flat(float* p, float* g, int64_t n, float lr, float grad_scale, int zero_grad, pbx_stream_t stream);
+int pbx_sigmoid_logloss(const float* logit, const float* label, int B, float* pred, float* loss_sum,
+                        float* dlogit, float gscale, pbx_stream_t stream);
+int pbx_fm_fwd(const float* x, int ldx, int B, int S, int E, int wcol, int vcol, int D, float* fm,
+               pbx_stream_t stream);
+int pbx_fm_bwd(const float* x, int ldx, const float* g, int B, int S, int E, int wcol, int vcol, int D, float* dx,
+               int lddx, int accumulate, pbx_stream_t stream);
+/* reference: operators/cvm_op.cu:29-75 */
+int pbx_cvm_fwd(const float* x, int64_t rows, int W, int use_cvm, float* y, pbx_stream_t stream);
+int pbx_cvm_bwd(const float* dy, const float* cvm, int64_t rows, int W, int use_cvm, float* dx,
+                pbx_stream_t stream);
+/* reference: operators/data_norm_op.cu:39-110 */
+int pbx_data_norm_fwd(const float* x, int64_t rows, int C, const float* bsize, const float* bsum, const float* bsq,
+                      float* y, float* means, float* scales, pbx_stream_t stream);
+int pbx_data_norm_bwd(const float* x, const float* dy, int64_t rows, int C, const float* means,
+                      const float* scales, float eps, float* dx, float* d_size, float* d_sum, float* d_sq,
+                      pbx_stream_t stream);
+/* reference: fleet/metrics.cc:115-136 (host bucketing) */
+int pbx_auc_bucket(const float* pred, const float* label, const float* mask, int64_t n, int nbuckets,
+                   double* table, double* sums, pbx_stream_t stream);
+/* reference: fleet/box_wrapper.cu:1210-1224 */
+int pbx_row_gather(const float* table, const int64_t* idx, int64_t n, int dim, float* out, pbx_stream_t stream);
+int pbx_l2_flush(void* buf, int64_t bytes, pbx_stream_t stream);
+
+/* ---- device-side batch construction (csrc/cuda/batch_build.cu) ----------------
+ * reference: data_feed.cu:1208-1384, data_feed.cc:3400-3522, :4896-4940 */
+int pbx_batch_build(const uint64_t* d_rec_keys, const int32_t* d_rec_off, int B, int S, uint64_t* d_keys_out,
+                    int32_t* d_lod_out, int32_t* d_scratch, pbx_stream_t stream);
+
+/* ---- symmetric memory + dense collectives (csrc/cuda/symm.cu) ------------------
+ * reference: boxps_worker.cc:1191-1258 (SyncParam), c_allreduce_x_op.cc:114-151,
+ * c_mixallgather_op.cc:221-328, transpiler/collective.py:240-315 */
+int pbx_symm_create(void** out, int rank, int nranks, uint64_t bytes);
+int pbx_symm_destroy(void* symm);
+void* pbx_symm_ptr(void* symm);
+int pbx_symm_ipc_handle(void* symm, void* out64);
+int pbx_symm_connect(void* symm, const void* handles);
+int pbx_symm_connect_local(void* symm, void* const* peers);
+int pbx_symm_status(void* symm, int* status, pbx_stream_t stream);
+int pbx_symm_collective(void* symm, int64_t off, int64_t n, float scale, int op, int root, int max_blocks,
+                        pbx_stream_t stream);
+int pbx_symm_collective_emu(void* const* symms, int nranks, int64_t off, int64_t n, float scale, int op,
+                            int root, pbx_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PBX_CUDA_H_ */
