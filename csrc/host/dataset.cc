@@ -1,0 +1,661 @@
+// See dataset.h for the reference map.
+#include "dataset.h"
+
+#include <dlfcn.h>
+#include <fcntl.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <sstream>
+
+namespace pbh {
+
+static thread_local std::string g_err;
+void set_error(const char* fmt, ...) {
+  char buf[1024];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+}
+const char* last_error() { return g_err.c_str(); }
+
+bool ThreadPool::set_cpu_affinity(std::thread& t, int core) {
+  cpu_set_t set;
+  CPU_ZERO(&set);
+  CPU_SET(core, &set);
+  return pthread_setaffinity_np(t.native_handle(), sizeof(set), &set) == 0;
+}
+
+// ---------------------------------------------------------------- KeyAgent
+void KeyAgent::add_keys(const uint64_t* keys, size_t n) {
+  const size_t S = shards_.size();
+  // bucket locally first so that each shard lock is taken once per call
+  thread_local std::vector<std::vector<uint64_t>> local;
+  if (local.size() != S) local.assign(S, {});
+  for (size_t i = 0; i < n; ++i) local[mix64(keys[i]) % S].push_back(keys[i]);
+  for (size_t s = 0; s < S; ++s) {
+    if (local[s].empty()) continue;
+    std::lock_guard<std::mutex> g(mu_[s]);
+    shards_[s].insert(shards_[s].end(), local[s].begin(), local[s].end());
+    local[s].clear();
+  }
+}
+
+void KeyAgent::finalize(ThreadPool* pool, std::vector<uint64_t>* out) {
+  pool->parallel_range(shards_.size(), [&](size_t b, size_t e, int) {
+    for (size_t s = b; s < e; ++s) {
+      auto& v = shards_[s];
+      std::sort(v.begin(), v.end());
+      v.erase(std::unique(v.begin(), v.end()), v.end());
+    }
+  });
+  size_t total = 0;
+  for (auto& v : shards_) total += v.size();
+  out->clear();
+  out->reserve(total);
+  for (auto& v : shards_) out->insert(out->end(), v.begin(), v.end());
+}
+
+// ---------------------------------------------------------------- batch dealing
+static void left_batches(int64_t ins_num, int nworkers, std::vector<BatchRange>* out, int64_t start) {
+  int64_t cur = start;
+  int64_t bs = ins_num / nworkers, left = ins_num % nworkers;
+  for (int i = 0; i < nworkers; ++i) {
+    int64_t n = bs + (i == 0 ? left : 0);
+    out->push_back({cur, (int)n});
+    cur += n;
+  }
+}
+
+void compute_batch_ranges(int64_t ins_num, int batch_size, int nworkers, std::vector<BatchRange>* out) {
+  out->clear();
+  const int64_t round = (int64_t)batch_size * nworkers;
+  if (round > ins_num) {  // less than one full round: split evenly
+    left_batches(ins_num, nworkers, out, 0);
+    return;
+  }
+  int64_t cur = 0;
+  int64_t full = ins_num / round * nworkers;
+  int64_t left = ins_num % round;
+  if (left > 0 && left < 2 * nworkers && full > 1) {
+    // tiny tail: fold it into the last full round and split that into two even rounds
+    full -= nworkers;
+    left += round;
+    for (int64_t i = 0; i < full; ++i) { out->push_back({cur, batch_size}); cur += batch_size; }
+    left_batches(left, nworkers * 2, out, cur);
+  } else {
+    for (int64_t i = 0; i < full; ++i) { out->push_back({cur, batch_size}); cur += batch_size; }
+    if (left > 0) left_batches(left, nworkers, out, cur);
+  }
+}
+
+// ---------------------------------------------------------------- Dataset
+Dataset::Dataset() : chan_(64) {}
+Dataset::~Dataset() {
+  wait_preload_done();
+  release_memory();
+  if (plugin_handle_) dlclose(plugin_handle_);
+}
+
+int Dataset::finalize_slots() {
+  sparse_idx_.assign(slots.size(), -1);
+  float_idx_.assign(slots.size(), -1);
+  float_dim_.clear();
+  float_off_.clear();
+  n_used_u64_ = n_used_f_ = 0;
+  dense_dim_ = 0;
+  for (size_t i = 0; i < slots.size(); ++i) {
+    if (!slots[i].is_used) continue;
+    if (slots[i].type == 0) {
+      sparse_idx_[i] = n_used_u64_++;
+    } else {
+      float_idx_[i] = n_used_f_++;
+      float_dim_.push_back(std::max(1, slots[i].dim));
+      float_off_.push_back(dense_dim_);
+      dense_dim_ += std::max(1, slots[i].dim);
+    }
+  }
+  // compact sparse_idx_ list of used sparse slots for n_sparse()
+  std::vector<int> used;
+  for (size_t i = 0; i < slots.size(); ++i) if (sparse_idx_[i] >= 0) used.push_back((int)i);
+  sparse_idx_.swap(used);  // now: list of slot indices that are used sparse slots
+  // rebuild per-slot lookup
+  slot_to_sparse_.assign(slots.size(), -1);
+  for (size_t p = 0; p < sparse_idx_.size(); ++p) slot_to_sparse_[sparse_idx_[p]] = (int)p;
+  if (!parser_plugin.empty() && !plugin_handle_) {
+    plugin_handle_ = dlopen(parser_plugin.c_str(), RTLD_NOW | RTLD_LOCAL);
+    PBH_REQUIRE(plugin_handle_ != nullptr, "cannot dlopen parser plugin %s: %s", parser_plugin.c_str(), dlerror());
+    plugin_fn_ = dlsym(plugin_handle_, "pbx_parse_line");
+    PBH_REQUIRE(plugin_fn_ != nullptr, "parser plugin %s lacks symbol pbx_parse_line", parser_plugin.c_str());
+  }
+  return 0;
+}
+
+static inline const char* skip_ws(const char* p, const char* e) {
+  while (p < e && (*p == ' ' || *p == '\t')) ++p;
+  return p;
+}
+
+static inline bool read_token(const char*& p, const char* e, const char** tb, size_t* tl) {
+  p = skip_ws(p, e);
+  if (p >= e) return false;
+  *tb = p;
+  while (p < e && *p != ' ' && *p != '\t' && *p != '\n' && *p != '\r') ++p;
+  *tl = (size_t)(p - *tb);
+  return *tl > 0;
+}
+
+static inline bool read_u64(const char*& p, const char* e, uint64_t* v) {
+  p = skip_ws(p, e);
+  if (p >= e || *p < '0' || *p > '9') return false;
+  uint64_t x = 0;
+  while (p < e && *p >= '0' && *p <= '9') { x = x * 10 + (uint64_t)(*p - '0'); ++p; }
+  *v = x;
+  return true;
+}
+
+static inline bool read_float(const char*& p, const char* e, float* v) {
+  p = skip_ws(p, e);
+  if (p >= e) return false;
+  char* end = nullptr;
+  *v = strtof(p, &end);
+  if (end == p) return false;
+  p = end;
+  return true;
+}
+
+// plugin ABI: the plugin parses one line and reports every slot through `emit`
+//   int pbx_parse_line(const char* line, size_t len, void* ctx,
+//                      void (*emit_u64)(void*, int slot, const uint64_t*, size_t),
+//                      void (*emit_f32)(void*, int slot, const float*, size_t),
+//                      void (*emit_meta)(void*, const char* ins_id, uint64_t search_id, uint32_t rank, uint32_t cmatch));
+// Role of the reference's ISlotParser .so plugins (data_feed.cc:3604-3670).
+struct PluginCtx {
+  std::vector<std::vector<uint64_t>> u64;
+  std::vector<std::vector<float>> f32;
+  std::string ins_id;
+  uint64_t search_id = 0;
+  uint32_t rank = 0, cmatch = 0;
+};
+typedef int (*plugin_fn_t)(const char*, size_t, void*, void (*)(void*, int, const uint64_t*, size_t),
+                           void (*)(void*, int, const float*, size_t),
+                           void (*)(void*, const char*, uint64_t, uint32_t, uint32_t));
+static void plug_emit_u64(void* c, int slot, const uint64_t* v, size_t n) {
+  auto* ctx = (PluginCtx*)c;
+  if (slot >= 0 && slot < (int)ctx->u64.size()) ctx->u64[slot].assign(v, v + n);
+}
+static void plug_emit_f32(void* c, int slot, const float* v, size_t n) {
+  auto* ctx = (PluginCtx*)c;
+  if (slot >= 0 && slot < (int)ctx->f32.size()) ctx->f32[slot].assign(v, v + n);
+}
+static void plug_emit_meta(void* c, const char* ins, uint64_t sid, uint32_t rank, uint32_t cmatch) {
+  auto* ctx = (PluginCtx*)c;
+  if (ins) ctx->ins_id = ins;
+  ctx->search_id = sid; ctx->rank = rank; ctx->cmatch = cmatch;
+}
+
+bool Dataset::parse_line(const char* line, size_t len, SlotRecord* rec) const {
+  const char* p = line;
+  const char* e = line + len;
+  while (e > p && (e[-1] == '\n' || e[-1] == '\r')) --e;
+  rec->reset();
+  rec->u64_offs.assign(n_used_u64_ + 1, 0);
+  rec->f_offs.assign(n_used_f_ + 1, 0);
+  thread_local std::vector<std::vector<uint64_t>> u64s;
+  thread_local std::vector<std::vector<float>> f32s;
+  u64s.resize(n_used_u64_);
+  f32s.resize(n_used_f_);
+  for (auto& v : u64s) v.clear();
+  for (auto& v : f32s) v.clear();
+
+  if (plugin_fn_) {
+    PluginCtx ctx;
+    ctx.u64.resize(slots.size());
+    ctx.f32.resize(slots.size());
+    if (((plugin_fn_t)plugin_fn_)(line, (size_t)(e - line), &ctx, plug_emit_u64, plug_emit_f32, plug_emit_meta) != 0)
+      return false;
+    rec->ins_id = ctx.ins_id; rec->search_id = ctx.search_id; rec->rank = ctx.rank; rec->cmatch = ctx.cmatch;
+    for (size_t s = 0; s < slots.size(); ++s) {
+      if (!slots[s].is_used) continue;
+      if (slots[s].type == 0) {
+        auto& dst = u64s[slot_to_sparse_[s]];
+        for (uint64_t v : ctx.u64[s]) if (v != 0 || slots[s].is_dense) dst.push_back(v);
+      } else {
+        auto& dst = f32s[float_idx_[s]];
+        for (float v : ctx.f32[s]) if (slots[s].is_dense || std::fabs(v) >= 1e-6f) dst.push_back(v);
+      }
+    }
+  } else {
+    const char* tb; size_t tl; uint64_t n;
+    if (parse_ins_id) {
+      if (!read_u64(p, e, &n) || n != 1 || !read_token(p, e, &tb, &tl)) return false;
+      rec->ins_id.assign(tb, tl);
+    }
+    if (parse_logkey) {
+      if (!read_u64(p, e, &n) || n != 1 || !read_token(p, e, &tb, &tl)) return false;
+      // logkey hex layout: [11,14) cmatch, [14,16) rank, [16,32) search_id (data_feed.cc:2385-2396)
+      if (tl >= 32) {
+        std::string lk(tb, tl);
+        rec->search_id = strtoull(lk.substr(16, 16).c_str(), nullptr, 16);
+        rec->cmatch = (uint32_t)strtoul(lk.substr(11, 3).c_str(), nullptr, 16);
+        rec->rank = (uint32_t)strtoul(lk.substr(14, 2).c_str(), nullptr, 16);
+      }
+    }
+    for (size_t s = 0; s < slots.size(); ++s) {
+      if (!read_u64(p, e, &n) || n == 0) return false;  // every slot needs >= 1 value (data_feed.cc:4086-4092)
+      const SlotDesc& sd = slots[s];
+      if (!sd.is_used) {  // skip token-wise
+        for (uint64_t i = 0; i < n; ++i) if (!read_token(p, e, &tb, &tl)) return false;
+        continue;
+      }
+      if (sd.type == 0) {
+        auto& dst = u64s[slot_to_sparse_[s]];
+        for (uint64_t i = 0; i < n; ++i) {
+          uint64_t v;
+          if (!read_u64(p, e, &v)) return false;
+          if (v != 0 || sd.is_dense) dst.push_back(v);  // zero feasigns dropped (data_feed.cc:4099)
+        }
+      } else {
+        auto& dst = f32s[float_idx_[s]];
+        for (uint64_t i = 0; i < n; ++i) {
+          float v;
+          if (!read_float(p, e, &v)) return false;
+          if (sd.is_dense || std::fabs(v) >= 1e-6f) dst.push_back(v);  // (data_feed.cc:4111)
+        }
+      }
+    }
+  }
+  size_t total_u64 = 0;
+  for (int s = 0; s < n_used_u64_; ++s) {
+    rec->u64_vals.insert(rec->u64_vals.end(), u64s[s].begin(), u64s[s].end());
+    total_u64 += u64s[s].size();
+    rec->u64_offs[s + 1] = (uint32_t)total_u64;
+  }
+  size_t total_f = 0;
+  for (int s = 0; s < n_used_f_; ++s) {
+    rec->f_vals.insert(rec->f_vals.end(), f32s[s].begin(), f32s[s].end());
+    total_f += f32s[s].size();
+    rec->f_offs[s + 1] = (uint32_t)total_f;
+  }
+  if (n_used_u64_ > 0 && total_u64 == 0) return false;  // no feasign at all (data_feed.cc:4133)
+  return true;
+}
+
+int Dataset::read_file(const std::string& path) {
+  FILE* fp = nullptr;
+  bool piped = false;
+  if (pipe_command.empty() || pipe_command == "cat") {
+    fp = fopen(path.c_str(), "r");
+  } else {
+    std::string cmd = "cat '" + path + "' | " + pipe_command;
+    fp = popen(cmd.c_str(), "r");
+    piped = true;
+  }
+  if (!fp) return -1;
+  std::vector<char> iobuf(4 << 20);  // 4 MB buffered reads (BufferedLineFileReader)
+  setvbuf(fp, iobuf.data(), _IOFBF, iobuf.size());
+  std::mt19937_64 rng(mix64(std::hash<std::string>()(path)));
+  std::uniform_real_distribution<float> uni(0.f, 1.f);
+  char* line = nullptr;
+  size_t cap = 0;
+  ssize_t len;
+  std::vector<SlotRecord*> block;
+  block.reserve(4096);
+  int64_t feas = 0;
+  while ((len = getline(&line, &cap, fp)) > 0) {
+    if (sample_rate < 1.0f && uni(rng) > sample_rate) continue;  // Bernoulli sampling
+    lines_read_++;
+    SlotRecord* rec = pool_.get();
+    if (!parse_line(line, (size_t)len, rec)) {
+      lines_bad_++;
+      std::vector<SlotRecord*> one{rec};
+      pool_.put(one);
+      continue;
+    }
+    feas += (int64_t)rec->u64_vals.size();
+    block.push_back(rec);
+    if (block.size() >= 4096) {
+      std::vector<SlotRecord*> out;
+      out.swap(block);
+      chan_.put(std::move(out));
+      block.reserve(4096);
+    }
+  }
+  if (!block.empty()) chan_.put(std::move(block));
+  free(line);
+  total_feasigns_ += feas;
+  if (piped) pclose(fp); else fclose(fp);
+  return 0;
+}
+
+void Dataset::reader_loop(std::atomic<size_t>* next_file, std::atomic<int>* errors) {
+  for (;;) {
+    size_t i = next_file->fetch_add(1);
+    // files are dealt round-robin over nodes first (SetFileList, data_set.cc:1963-1975)
+    size_t gi = i * (size_t)world + (size_t)rank;
+    if (gi >= files.size()) break;
+    if (read_file(files[gi]) != 0) (*errors)++;
+  }
+}
+
+void Dataset::merge_loop() {
+  std::vector<SlotRecord*> block;
+  std::vector<SlotRecord*> mine;
+  while (chan_.get(block)) {
+    if (collect_keys)
+      for (SlotRecord* r : block) agent_.add_keys(r->u64_vals.data(), r->u64_vals.size());
+    mine.insert(mine.end(), block.begin(), block.end());
+    block.clear();
+    if (mine.size() >= 65536) {
+      std::lock_guard<std::mutex> g(rec_mu_);
+      records_.insert(records_.end(), mine.begin(), mine.end());
+      mine.clear();
+    }
+  }
+  std::lock_guard<std::mutex> g(rec_mu_);
+  records_.insert(records_.end(), mine.begin(), mine.end());
+}
+
+int Dataset::load_into_memory() {
+  PBH_REQUIRE(!slots.empty(), "dataset has no slots (call set_use_var first)");
+  if (slot_to_sparse_.size() != slots.size()) {
+    int rc = finalize_slots();
+    if (rc) return rc;
+  }
+  Timer t;
+  t.start();
+  chan_.open();
+  agent_.clear();
+  if (collect_keys) agent_.add_key(0);  // key 0 is always registered (box_wrapper.h:1107)
+  std::atomic<size_t> next_file{0};
+  std::atomic<int> errors{0};
+  std::vector<std::thread> readers, mergers;
+  int nr = std::max(1, thread_num), nm = std::max(1, merge_thread_num);
+  for (int i = 0; i < nm; ++i) mergers.emplace_back([this] { merge_loop(); });
+  for (int i = 0; i < nr; ++i) readers.emplace_back([&] { reader_loop(&next_file, &errors); });
+  for (auto& th : readers) th.join();
+  chan_.close();
+  for (auto& th : mergers) th.join();
+  t.pause();
+  load_seconds_ = t.seconds();
+  Timer t2;
+  t2.start();
+  if (collect_keys) {
+    ThreadPool pool(nm);
+    agent_.finalize(&pool, &unique_keys_);
+    agent_.clear();
+  }
+  t2.pause();
+  merge_seconds_ = t2.seconds();
+  PBH_REQUIRE(errors.load() == 0, "%d input file(s) could not be opened", errors.load());
+  return 0;
+}
+
+int Dataset::preload_into_memory() {
+  wait_preload_done();
+  preload_rc_ = 0;
+  preload_thread_.reset(new std::thread([this] {
+    preload_rc_ = load_into_memory();
+    if (preload_rc_) preload_err_ = last_error();
+  }));
+  return 0;
+}
+
+int Dataset::wait_preload_done() {
+  if (preload_thread_) {
+    preload_thread_->join();
+    preload_thread_.reset();
+    if (preload_rc_) set_error("%s", preload_err_.c_str());
+    return preload_rc_;
+  }
+  return 0;
+}
+
+void Dataset::release_memory() {
+  pool_.put(records_);
+  records_.shrink_to_fit();
+  worker_batches_.clear();
+  unique_keys_.clear();
+  unique_keys_.shrink_to_fit();
+  total_feasigns_ = 0;
+  lines_read_ = 0;
+  lines_bad_ = 0;
+}
+
+void Dataset::local_shuffle(uint64_t seed) {
+  std::mt19937_64 rng(seed);
+  std::shuffle(records_.begin(), records_.end(), rng);
+}
+
+// AUC-runner: permute the feasigns of the chosen slots across records, keeping every other
+// slot in place, to measure how much the model relies on those slots
+// (reference RecordReplace / slots_shuffle, data_feed.h:1772-1962, box_wrapper.cc:212-368).
+int Dataset::slots_shuffle(const std::vector<int>& slot_idx, uint64_t seed) {
+  const size_t n = records_.size();
+  if (n < 2) return 0;
+  std::vector<size_t> perm(n);
+  for (size_t i = 0; i < n; ++i) perm[i] = i;
+  std::mt19937_64 rng(seed);
+  std::shuffle(perm.begin(), perm.end(), rng);
+  std::vector<char> chosen(n_used_u64_, 0);
+  for (int s : slot_idx) {
+    PBH_REQUIRE(s >= 0 && s < (int)slots.size() && slot_to_sparse_[s] >= 0, "slot %d is not a used sparse slot", s);
+    chosen[slot_to_sparse_[s]] = 1;
+  }
+  // snapshot donors' values of the chosen slots
+  std::vector<std::vector<std::vector<uint64_t>>> donor(n);
+  for (size_t i = 0; i < n; ++i) {
+    donor[i].resize(n_used_u64_);
+    const SlotRecord* r = records_[i];
+    for (int p = 0; p < n_used_u64_; ++p)
+      if (chosen[p]) donor[i][p].assign(r->u64_vals.begin() + r->u64_offs[p], r->u64_vals.begin() + r->u64_offs[p + 1]);
+  }
+  for (size_t i = 0; i < n; ++i) {
+    SlotRecord* r = records_[i];
+    std::vector<uint64_t> nv;
+    std::vector<uint32_t> no(n_used_u64_ + 1, 0);
+    for (int p = 0; p < n_used_u64_; ++p) {
+      if (chosen[p]) nv.insert(nv.end(), donor[perm[i]][p].begin(), donor[perm[i]][p].end());
+      else nv.insert(nv.end(), r->u64_vals.begin() + r->u64_offs[p], r->u64_vals.begin() + r->u64_offs[p + 1]);
+      no[p + 1] = (uint32_t)nv.size();
+    }
+    r->u64_vals.swap(nv);
+    r->u64_offs.swap(no);
+  }
+  return 0;
+}
+
+int Dataset::prepare_train(int nworkers, bool shuffle, uint64_t seed, int64_t min_batches) {
+  PBH_REQUIRE(nworkers >= 1, "nworkers must be >= 1");
+  if (enable_pv_merge) {
+    // page-view merge: instances of one search_id stay adjacent, ordered by rank (data_set.cc:2648-2688)
+    std::stable_sort(records_.begin(), records_.end(), [](const SlotRecord* a, const SlotRecord* b) {
+      return a->search_id != b->search_id ? a->search_id < b->search_id : a->rank < b->rank;
+    });
+  } else if (shuffle) {
+    local_shuffle(seed);
+  }
+  worker_batches_.assign(nworkers, {});
+  const int64_t n = (int64_t)records_.size();
+  if (n < nworkers) return 0;  // fewer instances than workers -> zero batches (data_set.cc:2696-2701)
+  std::vector<BatchRange> all;
+  compute_batch_ranges(n, batch_size, nworkers, &all);
+  for (size_t i = 0; i < all.size(); ++i) worker_batches_[i % nworkers].push_back(all[i]);
+  // multi-node equalisation: every rank must step the same number of times; the caller passes
+  // allreduce(max) of the local count and surplus batches are split (data_set.cc:2708-2750)
+  if (min_batches > 0) {
+    for (auto& wb : worker_batches_) {
+      while ((int64_t)wb.size() < min_batches && !wb.empty()) {
+        size_t big = 0;
+        for (size_t i = 1; i < wb.size(); ++i) if (wb[i].len > wb[big].len) big = i;
+        if (wb[big].len < 2) break;
+        BatchRange a = wb[big];
+        int h = a.len / 2;
+        wb[big] = {a.start, h};
+        wb.push_back({a.start + h, a.len - h});
+      }
+    }
+  }
+  return 0;
+}
+
+int Dataset::batch_shape(int worker, int64_t b, int* B, int64_t* n_keys) const {
+  PBH_REQUIRE(worker >= 0 && worker < (int)worker_batches_.size() && b >= 0 &&
+                  b < (int64_t)worker_batches_[worker].size(), "batch (%d, %lld) out of range", worker, (long long)b);
+  const BatchRange& r = worker_batches_[worker][b];
+  int64_t nk = 0;
+  for (int i = 0; i < r.len; ++i) nk += (int64_t)records_[r.start + i]->u64_vals.size();
+  *B = r.len;
+  *n_keys = nk;
+  return 0;
+}
+
+int Dataset::pack_batch(int worker, int64_t b, uint64_t* keys, int32_t* off, float* dense, int slot_major) const {
+  PBH_REQUIRE(worker >= 0 && worker < (int)worker_batches_.size() && b >= 0 &&
+                  b < (int64_t)worker_batches_[worker].size(), "batch (%d, %lld) out of range", worker, (long long)b);
+  const BatchRange& r = worker_batches_[worker][b];
+  const int B = r.len, S = n_used_u64_;
+  if (!slot_major) {
+    int64_t cur = 0;
+    for (int i = 0; i < B; ++i) {
+      const SlotRecord* rec = records_[r.start + i];
+      memcpy(keys + cur, rec->u64_vals.data(), rec->u64_vals.size() * sizeof(uint64_t));
+      int32_t* o = off + (int64_t)i * (S + 1);
+      for (int s = 0; s <= S; ++s) o[s] = (int32_t)(cur + rec->u64_offs[s]);
+      cur += (int64_t)rec->u64_vals.size();
+    }
+  } else {
+    int64_t cur = 0;
+    for (int s = 0; s < S; ++s) {
+      for (int i = 0; i < B; ++i) {
+        const SlotRecord* rec = records_[r.start + i];
+        off[(int64_t)s * B + i] = (int32_t)cur;
+        uint32_t a = rec->u64_offs[s], e = rec->u64_offs[s + 1];
+        memcpy(keys + cur, rec->u64_vals.data() + a, (size_t)(e - a) * sizeof(uint64_t));
+        cur += e - a;
+      }
+    }
+    off[(int64_t)S * B] = (int32_t)cur;
+  }
+  if (dense && dense_dim_ > 0) {
+    for (int i = 0; i < B; ++i) {
+      const SlotRecord* rec = records_[r.start + i];
+      float* d = dense + (int64_t)i * dense_dim_;
+      for (int f = 0; f < n_used_f_; ++f) {
+        uint32_t a = rec->f_offs[f], e = rec->f_offs[f + 1];
+        int dim = float_dim_[f];
+        for (int j = 0; j < dim; ++j) d[float_off_[f] + j] = (a + j < e) ? rec->f_vals[a + j] : 0.f;
+      }
+    }
+  }
+  return 0;
+}
+
+int Dataset::batch_ins_ids(int worker, int64_t b, std::string* joined) const {
+  PBH_REQUIRE(worker >= 0 && worker < (int)worker_batches_.size() && b >= 0 &&
+                  b < (int64_t)worker_batches_[worker].size(), "batch out of range");
+  const BatchRange& r = worker_batches_[worker][b];
+  joined->clear();
+  for (int i = 0; i < r.len; ++i) {
+    if (i) joined->push_back('\n');
+    joined->append(records_[r.start + i]->ins_id);
+  }
+  return 0;
+}
+
+int Dataset::batch_meta(int worker, int64_t b, uint64_t* search_ids, uint32_t* ranks, uint32_t* cmatch) const {
+  PBH_REQUIRE(worker >= 0 && worker < (int)worker_batches_.size() && b >= 0 &&
+                  b < (int64_t)worker_batches_[worker].size(), "batch out of range");
+  const BatchRange& r = worker_batches_[worker][b];
+  for (int i = 0; i < r.len; ++i) {
+    const SlotRecord* rec = records_[r.start + i];
+    if (search_ids) search_ids[i] = rec->search_id;
+    if (ranks) ranks[i] = rec->rank;
+    if (cmatch) cmatch[i] = rec->cmatch;
+  }
+  return 0;
+}
+
+// ---- binary archive: [magic][n_records] then per record
+//   search_id u64 | rank u32 | cmatch u32 | ins_len u32 | ins bytes |
+//   n_u64 u32 | u64 vals | n_offs u16 | offs u32[] | n_f u32 | f vals | n_foffs u16 | foffs u32[]
+static const uint64_t kArchiveMagic = 0x50425841524348ull;  // "PBXARCH"
+
+template <typename T>
+static void put(std::string& buf, const T& v) { buf.append((const char*)&v, sizeof(T)); }
+
+int Dataset::save_archive(const std::string& path) const {
+  FILE* fp = fopen(path.c_str(), "wb");
+  PBH_REQUIRE(fp != nullptr, "cannot open %s for writing", path.c_str());
+  std::string buf;
+  put(buf, kArchiveMagic);
+  put(buf, (uint64_t)records_.size());
+  for (const SlotRecord* r : records_) {
+    put(buf, r->search_id); put(buf, r->rank); put(buf, r->cmatch);
+    put(buf, (uint32_t)r->ins_id.size()); buf.append(r->ins_id);
+    put(buf, (uint32_t)r->u64_vals.size());
+    buf.append((const char*)r->u64_vals.data(), r->u64_vals.size() * 8);
+    put(buf, (uint16_t)r->u64_offs.size());
+    buf.append((const char*)r->u64_offs.data(), r->u64_offs.size() * 4);
+    put(buf, (uint32_t)r->f_vals.size());
+    buf.append((const char*)r->f_vals.data(), r->f_vals.size() * 4);
+    put(buf, (uint16_t)r->f_offs.size());
+    buf.append((const char*)r->f_offs.data(), r->f_offs.size() * 4);
+    if (buf.size() > (8u << 20)) { fwrite(buf.data(), 1, buf.size(), fp); buf.clear(); }
+  }
+  fwrite(buf.data(), 1, buf.size(), fp);
+  fclose(fp);
+  return 0;
+}
+
+int Dataset::load_archive(const std::string& path) {
+  FILE* fp = fopen(path.c_str(), "rb");
+  PBH_REQUIRE(fp != nullptr, "cannot open %s", path.c_str());
+  auto rd = [&](void* p, size_t n) { return fread(p, 1, n, fp) == n; };
+  uint64_t magic = 0, n = 0;
+  bool ok = rd(&magic, 8) && rd(&n, 8) && magic == kArchiveMagic;
+  if (slot_to_sparse_.size() != slots.size()) finalize_slots();
+  agent_.clear();
+  if (collect_keys) agent_.add_key(0);
+  for (uint64_t i = 0; ok && i < n; ++i) {
+    SlotRecord* r = pool_.get();
+    uint32_t len = 0, cnt = 0;
+    uint16_t no = 0;
+    ok = rd(&r->search_id, 8) && rd(&r->rank, 4) && rd(&r->cmatch, 4) && rd(&len, 4);
+    if (ok) { r->ins_id.resize(len); ok = len == 0 || rd(&r->ins_id[0], len); }
+    ok = ok && rd(&cnt, 4);
+    if (ok) { r->u64_vals.resize(cnt); ok = cnt == 0 || rd(r->u64_vals.data(), (size_t)cnt * 8); }
+    ok = ok && rd(&no, 2);
+    if (ok) { r->u64_offs.resize(no); ok = no == 0 || rd(r->u64_offs.data(), (size_t)no * 4); }
+    ok = ok && rd(&cnt, 4);
+    if (ok) { r->f_vals.resize(cnt); ok = cnt == 0 || rd(r->f_vals.data(), (size_t)cnt * 4); }
+    ok = ok && rd(&no, 2);
+    if (ok) { r->f_offs.resize(no); ok = no == 0 || rd(r->f_offs.data(), (size_t)no * 4); }
+    if (!ok) { std::vector<SlotRecord*> one{r}; pool_.put(one); break; }
+    if (collect_keys) agent_.add_keys(r->u64_vals.data(), r->u64_vals.size());
+    total_feasigns_ += (int64_t)r->u64_vals.size();
+    records_.push_back(r);
+  }
+  fclose(fp);
+  PBH_REQUIRE(ok, "archive %s is truncated or not a paddlebox_b200 archive", path.c_str());
+  if (collect_keys) {
+    ThreadPool pool(std::max(1, merge_thread_num));
+    agent_.finalize(&pool, &unique_keys_);
+    agent_.clear();
+  }
+  return 0;
+}
+
+std::string Dataset::last_stats() const {
+  std::ostringstream os;
+  os << "records=" << records_.size() << " lines=" << lines_read_.load() << " bad_lines=" << lines_bad_.load()
+     << " feasigns=" << total_feasigns_.load() << " unique_keys=" << unique_keys_.size()
+     << " read_s=" << load_seconds_ << " key_merge_s=" << merge_seconds_ << " pool_idle=" << 0;
+  return os.str();
+}
+
+}  // namespace pbh

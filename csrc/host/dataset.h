@@ -1,0 +1,159 @@
+// Pass-scoped in-memory SlotRecord dataset + data feed (host C++).
+// Reference roles: PadBoxSlotDataset / SlotRecordDataset (framework/data_set.cc:1905-2828,
+// :1853-1889), SlotPaddleBoxDataFeed (framework/data_feed.cc:2993-4153), SlotRecord /
+// SlotObjPool (framework/data_feed.h:96-428), BufferedLineFileReader (data_feed.cc:54-158),
+// PSAgent key collection (fleet/box_wrapper.cc:1185-1196, data_set.cc:2293-2349),
+// BinaryArchive (data_feed.cc:2824-2992), compute_batch_num (data_set.cc:280-331).
+#pragma once
+#include <memory>
+#include <random>
+#include <unordered_map>
+
+#include "util.h"
+
+namespace pbh {
+
+struct SlotDesc {
+  std::string name;
+  int type = 0;      // 0 = uint64 feasign slot, 1 = float slot
+  int is_dense = 0;  // dense: fixed `dim` values per instance
+  int is_used = 1;
+  int dim = 1;
+};
+
+// CSR-per-record: values of slot s are vals[offs[s] .. offs[s+1])
+struct SlotRecord {
+  uint64_t search_id = 0;
+  uint32_t rank = 0, cmatch = 0;
+  std::string ins_id;
+  std::vector<uint64_t> u64_vals;
+  std::vector<uint32_t> u64_offs;
+  std::vector<float> f_vals;
+  std::vector<uint32_t> f_offs;
+  void reset() {
+    search_id = 0; rank = cmatch = 0; ins_id.clear();
+    u64_vals.clear(); u64_offs.clear(); f_vals.clear(); f_offs.clear();
+  }
+};
+
+// Lock-protected free list with a capacity cap (FLAGS_padbox_record_pool_max_size).
+class RecordPool {
+ public:
+  explicit RecordPool(size_t cap = 2000000) : cap_(cap) {}
+  ~RecordPool() { for (auto* r : free_) delete r; }
+  SlotRecord* get() {
+    {
+      std::lock_guard<std::mutex> g(mu_);
+      if (!free_.empty()) { SlotRecord* r = free_.back(); free_.pop_back(); return r; }
+    }
+    return new SlotRecord();
+  }
+  void put(std::vector<SlotRecord*>& rs) {
+    std::lock_guard<std::mutex> g(mu_);
+    for (auto* r : rs) {
+      if (free_.size() < cap_) { r->reset(); free_.push_back(r); } else delete r;
+    }
+    rs.clear();
+  }
+  size_t idle() { std::lock_guard<std::mutex> g(mu_); return free_.size(); }
+ private:
+  std::mutex mu_;
+  std::vector<SlotRecord*> free_;
+  size_t cap_;
+};
+
+// Thread-sharded unique-key collector for the feed pass.
+class KeyAgent {
+ public:
+  explicit KeyAgent(int shards = 64) : shards_(shards), mu_(shards) {}
+  void add_keys(const uint64_t* keys, size_t n);
+  void add_key(uint64_t k) { add_keys(&k, 1); }
+  // sort+unique every shard (parallel) and concatenate
+  void finalize(ThreadPool* pool, std::vector<uint64_t>* out);
+  void clear() { for (auto& s : shards_) { s.clear(); s.shrink_to_fit(); } }
+ private:
+  std::vector<std::vector<uint64_t>> shards_;
+  std::vector<std::mutex> mu_;
+};
+
+struct BatchRange { int64_t start; int len; };
+
+class Dataset {
+ public:
+  Dataset();
+  ~Dataset();
+  // ---- configuration ----
+  std::vector<SlotDesc> slots;
+  std::vector<std::string> files;
+  std::string pipe_command = "cat";
+  std::string parser_plugin;       // path of a .so implementing the plugin ABI (see dataset.cc)
+  int thread_num = 1;              // reader threads
+  int merge_thread_num = 4;
+  int batch_size = 1;
+  bool parse_ins_id = false, parse_logkey = false;
+  float sample_rate = 1.0f;
+  bool enable_pv_merge = false;
+  bool collect_keys = true;
+  int rank = 0, world = 1;         // file round-robin across nodes (data_set.cc:1963-1975)
+
+  int finalize_slots();            // builds the used-slot index maps
+  // ---- pass lifecycle ----
+  int load_into_memory();
+  int preload_into_memory();       // async
+  int wait_preload_done();
+  void release_memory();
+  void local_shuffle(uint64_t seed);
+  int slots_shuffle(const std::vector<int>& slot_idx, uint64_t seed);  // AUC runner: permute slots across records
+  int prepare_train(int nworkers, bool shuffle, uint64_t seed, int64_t min_batches);
+  int64_t num_records() const { return (int64_t)records_.size(); }
+  int64_t num_batches(int worker) const { return worker < (int)worker_batches_.size() ? (int64_t)worker_batches_[worker].size() : 0; }
+  // sizes of one batch: instances and total uint64 feasigns of used sparse slots
+  int batch_shape(int worker, int64_t b, int* B, int64_t* n_keys) const;
+  // record-major CSR (device batch_build input): keys [n_keys], off [B*(S+1)] global offsets,
+  // dense [B, dense_dim]; or slot-major: keys in (slot, ins) order, off = lod [S*B+1]
+  int pack_batch(int worker, int64_t b, uint64_t* keys, int32_t* off, float* dense, int slot_major) const;
+  int batch_ins_ids(int worker, int64_t b, std::string* joined) const;
+  int batch_meta(int worker, int64_t b, uint64_t* search_ids, uint32_t* ranks, uint32_t* cmatch) const;
+  const std::vector<uint64_t>& unique_keys() const { return unique_keys_; }
+  int n_sparse() const { return (int)sparse_idx_.size(); }
+  int dense_dim() const { return dense_dim_; }
+  int64_t total_feasigns() const { return total_feasigns_.load(); }
+  // ---- archive (binary spill / reload; preload_into_disk) ----
+  int save_archive(const std::string& path) const;
+  int load_archive(const std::string& path);
+  std::string last_stats() const;
+
+  bool parse_line(const char* line, size_t len, SlotRecord* rec) const;
+
+ private:
+  void reader_loop(std::atomic<size_t>* next_file, std::atomic<int>* errors);
+  void merge_loop();
+  int read_file(const std::string& path);
+  std::vector<int> sparse_idx_;      // slot indices of the used uint64 sparse slots, in order
+  std::vector<int> slot_to_sparse_;  // slot index -> position among used sparse slots (-1 unused)
+  std::vector<int> float_idx_;       // slot index -> position among used float slots
+  std::string preload_err_;
+  std::vector<int> float_dim_;   // per used float slot: dense dim
+  std::vector<int> float_off_;   // per used float slot: offset into the dense row
+  int dense_dim_ = 0;
+  int n_used_u64_ = 0, n_used_f_ = 0;
+  std::vector<SlotRecord*> records_;
+  std::mutex rec_mu_;
+  RecordPool pool_;
+  Channel<std::vector<SlotRecord*>> chan_;
+  KeyAgent agent_;
+  std::vector<uint64_t> unique_keys_;
+  std::vector<std::vector<BatchRange>> worker_batches_;
+  std::unique_ptr<std::thread> preload_thread_;
+  int preload_rc_ = 0;
+  std::atomic<int64_t> total_feasigns_{0};
+  std::atomic<int64_t> lines_read_{0}, lines_bad_{0};
+  double load_seconds_ = 0, merge_seconds_ = 0;
+  void* plugin_handle_ = nullptr;
+  void* plugin_fn_ = nullptr;
+};
+
+// reference compute_batch_num (data_set.cc:280-331): every worker gets the same number of batches
+void compute_batch_ranges(int64_t ins_num, int batch_size, int nworkers, std::vector<BatchRange>* out);
+
+}  // namespace pbh

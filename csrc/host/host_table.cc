@@ -1,0 +1,383 @@
+// Host-memory tier of the sparse table + CPU execution of pull/push + checkpoint I/O.
+//
+// Roles in the reference: the closed libbox_ps.so memory tier (BeginPass stages the
+// pass's working set from host memory into HBM, EndPass writes it back; SaveBase /
+// SaveDelta / LoadSSD2Mem / ShrinkTable, fleet/box_wrapper.cc:171-210, :1286-1324) and its
+// open twin, pscore's MemorySparseTable + CtrDymfAccessor
+// (paddle/fluid/distributed/ps/table/memory_sparse_table.cc:338-393,
+// ctr_dymf_accessor.cc:68-142, :279-315).  The CPU optimizer math restates
+// heter_ps/optimizer.cuh.h:30-472 and must match csrc/cuda/table.cuh bit-for-bit in
+// structure (same layout, same update order).
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <sstream>
+#include <unordered_map>
+
+#include "../../include/pbx_types.h"
+#include "util.h"
+
+namespace pbh {
+
+static inline float uniform01(uint64_t key, uint32_t idx, uint64_t seed) {
+  uint64_t x = mix64(key + 0x632be59bd9b4e019ull * (uint64_t)(idx + 1) + seed);
+  return ((float)((x >> 40) + 1)) * (1.0f / 16777216.0f);
+}
+
+class HostTable {
+ public:
+  HostTable(int embedx_dim, int optimizer, const PbxSparseOptConfig& cfg, uint64_t seed, int shards)
+      : L(pbx_make_layout(embedx_dim, optimizer)), cfg(cfg), seed(seed), shards_(shards), mu_(shards) {}
+
+  PbxRowLayout L;
+  PbxSparseOptConfig cfg;
+  uint64_t seed;
+  bool test_mode = false;
+
+  struct Shard {
+    std::unordered_map<uint64_t, uint32_t> index;
+    std::vector<float> rows;
+    std::vector<uint64_t> keys;
+    std::vector<uint8_t> dirty;
+  };
+
+  size_t shard_of(uint64_t k) const { return mix64(k ^ 0x5bd1e995u) % shards_.size(); }
+
+  size_t size() const {
+    size_t n = 0;
+    for (auto& s : shards_) n += s.keys.size();
+    return n;
+  }
+
+  void init_row(float* row, uint64_t key) const {
+    std::fill(row, row + L.stride, 0.f);
+    row[2] = cfg.initial_range != 0.f ? uniform01(key, 0xffffu, seed) * cfg.initial_range : 0.f;
+    if (L.optimizer != PBX_OPT_ADAGRAD) {
+      row[L.off_es + 2] = cfg.beta1_decay_rate;
+      row[L.off_es + 3] = cfg.beta2_decay_rate;
+    }
+  }
+
+  float* find_or_create(uint64_t key, bool create, bool* fresh = nullptr) {
+    Shard& s = shards_[shard_of(key)];
+    auto it = s.index.find(key);
+    if (fresh) *fresh = false;
+    if (it != s.index.end()) return s.rows.data() + (size_t)it->second * L.stride;
+    if (!create) return nullptr;
+    uint32_t idx = (uint32_t)s.keys.size();
+    s.index.emplace(key, idx);
+    s.keys.push_back(key);
+    s.dirty.push_back(0);
+    s.rows.resize(s.rows.size() + L.stride);
+    float* row = s.rows.data() + (size_t)idx * L.stride;
+    init_row(row, key);
+    if (fresh) *fresh = true;
+    return row;
+  }
+
+  // full rows for HBM staging; missing keys are created with initial state
+  void fetch_rows(const uint64_t* keys, int64_t n, float* out, bool create, ThreadPool* pool) {
+    // group by shard to lock each shard once per worker
+    run_sharded(keys, n, pool, [&](Shard&, int64_t i) {
+      float* row = find_or_create(keys[i], create);
+      if (row) memcpy(out + i * L.stride, row, L.stride * sizeof(float));
+      else init_row(out + i * L.stride, keys[i]);
+    });
+  }
+
+  void store_rows(const uint64_t* keys, int64_t n, const float* rows, bool mark_dirty, ThreadPool* pool) {
+    run_sharded(keys, n, pool, [&](Shard& s, int64_t i) {
+      float* row = find_or_create(keys[i], true);
+      memcpy(row, rows + i * L.stride, L.stride * sizeof(float));
+      if (mark_dirty) s.dirty[s.index[keys[i]]] = 1;
+    });
+  }
+
+  // CPU pull records [n, hidden] (key 0 / unknown keys -> zeros)
+  void pull(const uint64_t* keys, int64_t n, float* out, int out_stride, ThreadPool* pool) {
+    const int H = 3 + L.embedx_dim;
+    run_sharded(keys, n, pool, [&](Shard&, int64_t i) {
+      float* o = out + i * out_stride;
+      float* row = keys[i] == 0 ? nullptr : find_or_create(keys[i], false);
+      if (!row) { std::fill(o, o + out_stride, 0.f); return; }
+      memcpy(o, row, H * sizeof(float));
+      for (int j = H; j < out_stride; ++j) o[j] = 0.f;
+    });
+  }
+
+  // CPU push of merged records for unique keys
+  void push(const uint64_t* keys, int64_t n, const float* push, int push_stride, ThreadPool* pool) {
+    if (test_mode) return;
+    run_sharded(keys, n, pool, [&](Shard& s, int64_t i) {
+      if (keys[i] == 0) return;
+      float* row = find_or_create(keys[i], false);
+      if (!row) return;
+      apply_push(row, keys[i], push + i * push_stride);
+      s.dirty[s.index[keys[i]]] = 1;
+    });
+  }
+
+  void adagrad(float* w, float* g2sum, const float* g, int n, float scale, float lr, float g2_0, float lo,
+               float hi) const {
+    float ratio = lr * std::sqrt(g2_0 / (g2_0 + *g2sum));
+    float add = 0.f, inv = 1.f / scale;
+    for (int i = 0; i < n; ++i) {
+      float sg = g[i] * inv;
+      w[i] = std::min(std::max(w[i] + sg * ratio, lo), hi);
+      add += sg * sg;
+    }
+    *g2sum += add / (float)n;
+  }
+
+  void adam(float* w, float* m, float* v, float* b1p, float* b2p, const float* g, int n, float scale, float lr,
+            float b1, float b2, float eps, float lo, float hi, bool shared) const {
+    float b1pow = *b1p, b2pow = *b2p;
+    float ratio = lr * std::sqrt(1.f - b2pow) / (1.f - b1pow);
+    float inv = 1.f / scale;
+    float sm = 0.f, sv = 0.f, m0 = *m, v0 = *v;
+    for (int i = 0; i < n; ++i) {
+      float sg = g[i] * inv;
+      float mi = shared ? m0 : m[i], vi = shared ? v0 : v[i];
+      float nm = b1 * mi + (1.f - b1) * sg;
+      float nv = b2 * vi + (1.f - b2) * sg * sg;
+      w[i] = std::min(std::max(w[i] + ratio * (nm / (std::sqrt(nv) + eps)), lo), hi);
+      if (!shared) { m[i] = nm; v[i] = nv; }
+      sm += nm; sv += nv;
+    }
+    if (shared) { *m = sm / (float)n; *v = sv / (float)n; }
+    *b1p = b1pow * b1;
+    *b2p = b2pow * b2;
+  }
+
+  void apply_push(float* row, uint64_t key, const float* push) const {
+    const PbxSparseOptConfig& c = cfg;
+    float g_show = push[1], g_click = push[2];
+    if (g_show <= 0.f) return;
+    row[L.off_tail + 1] = push[0];
+    float show = row[0] + g_show, click = row[1] + g_click;
+    row[0] = show; row[1] = click;
+    row[L.off_tail + 0] += c.nonclk_coeff * (g_show - g_click) + c.clk_coeff * g_click;
+    row[L.off_tail + 2] = 0.f;
+    float* es = row + L.off_es;
+    float* xs = row + L.off_xs;
+    const int D = L.embedx_dim;
+    if (L.optimizer == PBX_OPT_ADAGRAD)
+      adagrad(row + 2, es, push + 3, 1, g_show, c.learning_rate, c.initial_g2sum, c.min_bound, c.max_bound);
+    else
+      adam(row + 2, es, es + 1, es + 2, es + 3, push + 3, 1, g_show, c.learning_rate, c.beta1_decay_rate,
+           c.beta2_decay_rate, c.ada_epsilon, c.min_bound, c.max_bound, false);
+    if (row[L.off_mf] == 0.f) {
+      if (c.mf_create_thresholds <= c.nonclk_coeff * (show - click) + c.clk_coeff * click) {
+        row[L.off_mf] = (float)D;
+        for (int i = 0; i < D; ++i) row[3 + i] = uniform01(key, (uint32_t)i, seed) * c.mf_initial_range;
+        if (L.optimizer == PBX_OPT_ADAM) { xs[2 * D] = c.mf_beta1_decay_rate; xs[2 * D + 1] = c.mf_beta2_decay_rate; }
+        else if (L.optimizer == PBX_OPT_SHARED_ADAM) { xs[2] = c.mf_beta1_decay_rate; xs[3] = c.mf_beta2_decay_rate; }
+      }
+    } else if (L.optimizer == PBX_OPT_ADAGRAD) {
+      adagrad(row + 3, xs, push + 4, D, g_show, c.mf_learning_rate, c.mf_initial_g2sum, c.mf_min_bound,
+              c.mf_max_bound);
+    } else if (L.optimizer == PBX_OPT_ADAM) {
+      adam(row + 3, xs, xs + D, xs + 2 * D, xs + 2 * D + 1, push + 4, D, g_show, c.mf_learning_rate,
+           c.mf_beta1_decay_rate, c.mf_beta2_decay_rate, c.mf_ada_epsilon, c.mf_min_bound, c.mf_max_bound, false);
+    } else {
+      adam(row + 3, xs, xs + 1, xs + 2, xs + 3, push + 4, D, g_show, c.mf_learning_rate, c.mf_beta1_decay_rate,
+           c.mf_beta2_decay_rate, c.mf_ada_epsilon, c.mf_min_bound, c.mf_max_bound, true);
+    }
+  }
+
+  // decay + evict (CtrDymfAccessor::Shrink); returns survivors
+  int64_t shrink(float decay, float delete_threshold, float delete_after_unseen_days) {
+    int64_t kept = 0;
+    for (auto& s : shards_) {
+      Shard ns;
+      for (size_t i = 0; i < s.keys.size(); ++i) {
+        float* row = s.rows.data() + i * L.stride;
+        row[0] *= decay;
+        row[1] *= decay;
+        row[L.off_tail + 2] += 1.f;
+        float score = cfg.nonclk_coeff * (row[0] - row[1]) + cfg.clk_coeff * row[1];
+        bool evict = s.keys[i] != 0 && (score < delete_threshold || row[L.off_tail + 2] > delete_after_unseen_days);
+        if (evict) continue;
+        ns.index.emplace(s.keys[i], (uint32_t)ns.keys.size());
+        ns.keys.push_back(s.keys[i]);
+        ns.dirty.push_back(s.dirty[i]);
+        ns.rows.insert(ns.rows.end(), row, row + L.stride);
+      }
+      kept += (int64_t)ns.keys.size();
+      s = std::move(ns);
+    }
+    return kept;
+  }
+
+  // ---- text checkpoint, one directory per table, files part-<shard>-<file>
+  // line: "<key> <unseen_days> <delta_score> <show> <click> <embed_w> <embed_state...> <slot> <mf_dim>
+  //        [<embedx_state...> <embedx_w...>]"   (ctr_dymf_accessor.cc:279-315)
+  // mode 0 = all (batch model, full state), 1 = delta (dirty rows, serving format),
+  //      2 = base (serving format: no optimizer state), 3 = batch model
+  int save(const std::string& dir, int mode, int part_shard_base, float base_threshold, float delta_threshold,
+           int64_t* n_saved, bool clear_dirty) {
+    int64_t total = 0;
+    for (size_t si = 0; si < shards_.size(); ++si) {
+      Shard& s = shards_[si];
+      char name[512];
+      snprintf(name, sizeof(name), "%s/part-%03d-%05d", dir.c_str(), part_shard_base, (int)si);
+      FILE* fp = fopen(name, "w");
+      PBH_REQUIRE(fp != nullptr, "cannot open %s for writing", name);
+      for (size_t i = 0; i < s.keys.size(); ++i) {
+        const float* row = s.rows.data() + i * L.stride;
+        float score = cfg.nonclk_coeff * (row[0] - row[1]) + cfg.clk_coeff * row[1];
+        if (mode == 1 && !(s.dirty[i] && score >= delta_threshold)) continue;
+        if (mode == 2 && score < base_threshold) continue;
+        const bool serving = (mode == 1 || mode == 2);
+        const int D = L.embedx_dim;
+        const bool has_mf = row[L.off_mf] != 0.f;
+        fprintf(fp, "%llu %g %g %g %g %.9g", (unsigned long long)s.keys[i], row[L.off_tail + 2], row[L.off_tail + 0],
+                row[0], row[1], row[2]);
+        if (!serving) for (int j = 0; j < L.embed_state; ++j) fprintf(fp, " %.9g", row[L.off_es + j]);
+        fprintf(fp, " %d %d", (int)row[L.off_tail + 1], has_mf ? D : 0);
+        if (has_mf) {
+          if (!serving) for (int j = 0; j < L.embedx_state; ++j) fprintf(fp, " %.9g", row[L.off_xs + j]);
+          for (int j = 0; j < D; ++j) fprintf(fp, " %.9g", row[3 + j]);
+        }
+        fputc('\n', fp);
+        ++total;
+        if (clear_dirty && mode == 1) s.dirty[i] = 0;
+      }
+      fclose(fp);
+    }
+    if (n_saved) *n_saved = total;
+    return 0;
+  }
+
+  // loads files written by save() with mode 0/3 (full state); serving-format files restore
+  // weights with fresh optimizer state.
+  int load_file(const std::string& path, bool serving, int64_t* n_loaded) {
+    FILE* fp = fopen(path.c_str(), "r");
+    PBH_REQUIRE(fp != nullptr, "cannot open %s", path.c_str());
+    char* line = nullptr;
+    size_t cap = 0;
+    ssize_t len;
+    int64_t cnt = 0;
+    const int D = L.embedx_dim;
+    while ((len = getline(&line, &cap, fp)) > 0) {
+      char* p = line;
+      uint64_t key = strtoull(p, &p, 10);
+      std::vector<float> f;
+      for (;;) {
+        char* e = nullptr;
+        float v = strtof(p, &e);
+        if (e == p) break;
+        f.push_back(v);
+        p = e;
+      }
+      size_t need = 5 + (serving ? 0 : L.embed_state) + 2;
+      if (f.size() < need) continue;
+      float* row = find_or_create(key, true);
+      init_row(row, key);
+      size_t q = 0;
+      row[L.off_tail + 2] = f[q++];
+      row[L.off_tail + 0] = f[q++];
+      row[0] = f[q++]; row[1] = f[q++]; row[2] = f[q++];
+      if (!serving) for (int j = 0; j < L.embed_state; ++j) row[L.off_es + j] = f[q++];
+      row[L.off_tail + 1] = f[q++];
+      int mf = (int)f[q++];
+      if (mf > 0 && f.size() >= q + (serving ? 0 : L.embedx_state) + D) {
+        row[L.off_mf] = (float)D;
+        if (!serving) for (int j = 0; j < L.embedx_state; ++j) row[L.off_xs + j] = f[q++];
+        else if (L.optimizer == PBX_OPT_ADAM) { row[L.off_xs + 2 * D] = cfg.mf_beta1_decay_rate; row[L.off_xs + 2 * D + 1] = cfg.mf_beta2_decay_rate; }
+        else if (L.optimizer == PBX_OPT_SHARED_ADAM) { row[L.off_xs + 2] = cfg.mf_beta1_decay_rate; row[L.off_xs + 3] = cfg.mf_beta2_decay_rate; }
+        for (int j = 0; j < D; ++j) row[3 + j] = f[q++];
+      }
+      ++cnt;
+    }
+    free(line);
+    fclose(fp);
+    if (n_loaded) *n_loaded = cnt;
+    return 0;
+  }
+
+  void all_keys(std::vector<uint64_t>* out) const {
+    out->clear();
+    for (auto& s : shards_) out->insert(out->end(), s.keys.begin(), s.keys.end());
+  }
+
+  void clear() { for (auto& s : shards_) s = Shard(); }
+
+ private:
+  template <typename F>
+  void run_sharded(const uint64_t* keys, int64_t n, ThreadPool* pool, F fn) {
+    const size_t S = shards_.size();
+    if (!pool || n < 4096) {
+      for (int64_t i = 0; i < n; ++i) fn(shards_[shard_of(keys[i])], i);
+      return;
+    }
+    // each worker owns a disjoint set of shards -> no locks on the maps
+    int W = pool->size();
+    pool->parallel_range((size_t)W, [&](size_t wb, size_t we, int) {
+      for (size_t w = wb; w < we; ++w)
+        for (int64_t i = 0; i < n; ++i) {
+          size_t sh = shard_of(keys[i]);
+          if (sh % (size_t)W == w) fn(shards_[sh], i);
+        }
+    });
+    (void)S;
+  }
+  std::vector<Shard> shards_;
+  std::vector<std::mutex> mu_;
+};
+
+}  // namespace pbh
+
+using pbh::HostTable;
+static pbh::ThreadPool* table_pool() {
+  static pbh::ThreadPool pool((int)std::max(2u, std::min(16u, std::thread::hardware_concurrency())));
+  return &pool;
+}
+
+extern "C" {
+
+int pbh_table_create(void** out, int embedx_dim, int optimizer, const PbxSparseOptConfig* cfg, uint64_t seed) {
+  *out = new HostTable(embedx_dim, optimizer, *cfg, seed, 64);
+  return 0;
+}
+int pbh_table_destroy(void* h) { delete (HostTable*)h; return 0; }
+int64_t pbh_table_size(void* h) { return (int64_t)((HostTable*)h)->size(); }
+int pbh_table_set_config(void* h, const PbxSparseOptConfig* cfg) { ((HostTable*)h)->cfg = *cfg; return 0; }
+int pbh_table_set_test_mode(void* h, int on) { ((HostTable*)h)->test_mode = on != 0; return 0; }
+int pbh_table_clear(void* h) { ((HostTable*)h)->clear(); return 0; }
+int pbh_table_fetch_rows(void* h, const uint64_t* keys, int64_t n, float* out, int create) {
+  ((HostTable*)h)->fetch_rows(keys, n, out, create != 0, table_pool());
+  return 0;
+}
+int pbh_table_store_rows(void* h, const uint64_t* keys, int64_t n, const float* rows, int mark_dirty) {
+  ((HostTable*)h)->store_rows(keys, n, rows, mark_dirty != 0, table_pool());
+  return 0;
+}
+int pbh_table_pull(void* h, const uint64_t* keys, int64_t n, float* out, int out_stride) {
+  ((HostTable*)h)->pull(keys, n, out, out_stride, table_pool());
+  return 0;
+}
+int pbh_table_push(void* h, const uint64_t* keys, int64_t n, const float* push, int push_stride) {
+  ((HostTable*)h)->push(keys, n, push, push_stride, table_pool());
+  return 0;
+}
+int64_t pbh_table_shrink(void* h, float decay, float delete_threshold, float delete_after_unseen_days) {
+  return ((HostTable*)h)->shrink(decay, delete_threshold, delete_after_unseen_days);
+}
+int pbh_table_save(void* h, const char* dir, int mode, int part_shard_base, float base_threshold,
+                   float delta_threshold, int clear_dirty, int64_t* n_saved) {
+  return ((HostTable*)h)->save(dir, mode, part_shard_base, base_threshold, delta_threshold, n_saved,
+                               clear_dirty != 0);
+}
+int pbh_table_load_file(void* h, const char* path, int serving, int64_t* n_loaded) {
+  return ((HostTable*)h)->load_file(path, serving != 0, n_loaded);
+}
+int64_t pbh_table_keys(void* h, uint64_t* out, int64_t max_n) {
+  std::vector<uint64_t> ks;
+  ((HostTable*)h)->all_keys(&ks);
+  int64_t n = std::min<int64_t>(max_n, (int64_t)ks.size());
+  if (out && n > 0) memcpy(out, ks.data(), (size_t)n * 8);
+  return (int64_t)ks.size();
+}
+
+}  // extern "C"

@@ -1,0 +1,103 @@
+"""Runtime flag registry (the reference's exported gflags).
+
+Every flag can be set from the environment as ``FLAGS_<name>`` before import, or at run
+time with ``set_flags({...})`` / ``FLAGS.<name> = v`` — the same two channels Paddle's
+``PADDLE_DEFINE_EXPORTED_*`` flags offer (paddle/fluid/platform/flags.cc:929-1011,
+framework/boxps_worker.cc:43-58, framework/data_set.cc:42).
+"""
+from __future__ import annotations
+
+import os
+from typing import Any
+
+
+class _Flags:
+    def __init__(self):
+        object.__setattr__(self, "_defs", {})
+        object.__setattr__(self, "_vals", {})
+
+    def define(self, name: str, default: Any, doc: str = "") -> None:
+        self._defs[name] = (type(default), default, doc)
+        env = os.environ.get("FLAGS_" + name)
+        self._vals[name] = self._parse(name, env) if env is not None else default
+
+    def _parse(self, name: str, text: Any) -> Any:
+        typ = self._defs[name][0]
+        if isinstance(text, typ) and not (typ is int and isinstance(text, bool)):
+            return text
+        if typ is bool:
+            if isinstance(text, (int, float)):
+                return bool(text)
+            return str(text).strip().lower() in ("1", "true", "yes", "on")
+        return typ(text)
+
+    def __getattr__(self, name: str) -> Any:
+        try:
+            return self._vals[name]
+        except KeyError:
+            raise AttributeError(f"unknown flag {name!r}") from None
+
+    def __setattr__(self, name: str, value: Any) -> None:
+        if name not in self._defs:
+            raise AttributeError(f"unknown flag {name!r}")
+        self._vals[name] = self._parse(name, value)
+
+    def names(self):
+        return sorted(self._defs)
+
+    def describe(self) -> str:
+        return "\n".join(f"{n} = {self._vals[n]!r}  # {self._defs[n][2]}" for n in self.names())
+
+
+FLAGS = _Flags()
+_d = FLAGS.define
+
+# --- pull / push -------------------------------------------------------------
+_d("enable_pullpush_dedup_keys", True, "dedup keys before pull/push (flags.cc:946)")
+_d("enable_pull_box_padding_zero", True, "empty slot -> one zero row (pull_box_sparse_op.h:131-147)")
+_d("gpugraph_hbm_table_load_factor", 0.75, "max load factor of the HBM table")
+_d("gpugraph_enable_gpu_direct_access", True, "owner writes requester buffers through peer pointers (always on here)")
+_d("gpugraph_enable_segment_merge_grads", False, "two-level gradient merge for hot keys")
+_d("gpugraph_merge_grads_segment_size", 128, "segment size of the two-level merge")
+_d("gpugraph_dedup_pull_push_mode", 1, "dedup mode")
+# --- dense sync ------------------------------------------------------------------
+_d("enable_sync_dense_moment", False, "also average Adam moments in K-step sync (boxps_worker.cc:468-475)")
+_d("enable_dense_nccl_barrier", False, "barrier before dense sync")
+_d("padbox_enable_sharding_stage", False, "ZeRO-1 style dense sharding (boxps_worker.cc:53-56)")
+_d("dense_use_nccl", False, "use the NCCL baseline path instead of the symmetric-memory collectives")
+# --- dataset -----------------------------------------------------------------------
+_d("enable_binding_train_cpu", True, "pin worker threads to cores (boxps_trainer.cc:165-193)")
+_d("enable_shuffle_by_searchid", False, "hash records by search_id in global shuffle")
+_d("enable_ins_parser_file", False, "parser plugin consumes whole files")
+_d("padbox_record_pool_max_size", 2000000, "SlotRecord object pool cap (data_feed.h:241-428)")
+_d("padbox_slotrecord_extend_dim", 0, "extra floats appended to each record")
+_d("padbox_dataset_shuffle_thread_num", 20, "shuffle threads")
+_d("padbox_dataset_merge_thread_num", 20, "merge / key-collection threads")
+_d("padbox_dataset_disable_shuffle", False, "skip cross-node shuffle")
+_d("padbox_dataset_disable_polling", False, "round-robin file assignment instead of polling")
+_d("padbox_disable_ins_shuffle", False, "keep instance order in PrepareTrain (data_set.cc:42)")
+_d("padbox_auc_runner_mode", False, "slot-shuffle feature evaluation mode")
+_d("use_gpu_replica_cache", False, "enable GpuReplicaCache")
+_d("gpu_replica_cache_dim", 8, "row width of the replica cache")
+_d("fix_dayid", False, "do not advance the day id between passes")
+# --- worker -----------------------------------------------------------------------
+_d("padbox_enable_gc", True, "eager free of dead activations")
+_d("padbox_enable_print_op_debug", False, "log every op before it runs")
+_d("padbox_dump_debug_lineid", "", "dump only this line id")
+_d("enable_dump_main_program", False, "write the per-device op list to ./device_<id>_ops.txt")
+_d("check_nan_inf", False, "abort + dump on NaN/Inf in a batch (boxps_worker.cc:1325-1336)")
+_d("enable_debug_print_metrics_info", False, "verbose AUC computation (metrics.cc:29-31)")
+# --- this framework -------------------------------------------------------------------
+_d("pbx_use_cuda_graph", True, "capture the training step in a CUDA graph when shapes allow")
+_d("pbx_sparse_cap_factor", 2.0, "mailbox capacity = factor * max_keys / nranks")
+
+
+def set_flags(d: dict) -> None:
+    for k, v in d.items():
+        setattr(FLAGS, k[6:] if k.startswith("FLAGS_") else k, v)
+
+
+def get_flags(names) -> dict:
+    if isinstance(names, str):
+        names = [names]
+    return {n: getattr(FLAGS, n[6:] if n.startswith("FLAGS_") else n) for n in names}

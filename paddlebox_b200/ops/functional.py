@@ -1,0 +1,201 @@
+"""Differentiable CTR building blocks backed by csrc/cuda/dense_ops.cu (CUDA tensors) or
+the PyTorch oracles in ``ops/reference.py`` (CPU tensors).
+
+  continuous_value_model  — reference ``cvm`` op (operators/cvm_op.cu:29-75; layers/nn.py:14947)
+  data_norm / DataNorm    — reference ``data_norm`` op (operators/data_norm_op.cu:39-265)
+  fm_interaction          — DeepFM first + second order head
+  sigmoid_log_loss        — sigmoid + log_loss (mean) with the gradient produced in the same pass
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+import torch.nn as nn
+
+from .. import _native as N
+from . import reference as R
+
+
+# ------------------------------------------------------------------ cvm
+class _CVM(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, cvm, use_cvm):
+        ctx.save_for_backward(cvm)
+        ctx.meta = (x.shape[1], use_cvm)
+        if not x.is_cuda:
+            return R.cvm_fwd(x, use_cvm)
+        x = x.contiguous()
+        rows, W = x.shape
+        y = torch.empty(rows, W if use_cvm else W - 2, dtype=x.dtype, device=x.device)
+        N.check(N.cuda().pbx_cvm_fwd(N.ptr(x), C.c_int64(rows), W, int(use_cvm), N.ptr(y), N.stream_ptr()))
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (cvm,) = ctx.saved_tensors
+        W, use_cvm = ctx.meta
+        if not dy.is_cuda:
+            return R.cvm_bwd(dy, cvm, W, use_cvm), None, None
+        dy = dy.contiguous()
+        dx = torch.empty(dy.shape[0], W, dtype=dy.dtype, device=dy.device)
+        N.check(N.cuda().pbx_cvm_bwd(N.ptr(dy), N.ptr(cvm.contiguous()), C.c_int64(dy.shape[0]), W, int(use_cvm),
+                                     N.ptr(dx), N.stream_ptr()))
+        return dx, None, None
+
+
+def continuous_value_model(x: torch.Tensor, cvm: torch.Tensor, use_cvm: bool = True) -> torch.Tensor:
+    """x: [rows, W] with (show, click) in columns 0..1; cvm: [rows, 2] show/click labels
+    that replace the first two gradient columns in backward."""
+    return _CVM.apply(x, cvm, use_cvm)
+
+
+# ------------------------------------------------------------------ data_norm
+class _DataNorm(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, bsize, bsum, bsq, eps, stat_sink):
+        if not x.is_cuda:
+            y, mean, scale = R.data_norm_fwd(x, bsize, bsum, bsq)
+        else:
+            x = x.contiguous()
+            rows, Cc = x.shape
+            y = torch.empty_like(x)
+            mean = torch.empty(Cc, dtype=torch.float32, device=x.device)
+            scale = torch.empty(Cc, dtype=torch.float32, device=x.device)
+            N.check(N.cuda().pbx_data_norm_fwd(N.ptr(x), C.c_int64(rows), Cc, N.ptr(bsize), N.ptr(bsum), N.ptr(bsq),
+                                               N.ptr(y), N.ptr(mean), N.ptr(scale), N.stream_ptr()))
+        ctx.save_for_backward(x, mean, scale)
+        ctx.eps = eps
+        ctx.sink = stat_sink
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, mean, scale = ctx.saved_tensors
+        if not dy.is_cuda:
+            dx, d_size, d_sum, d_sq = R.data_norm_bwd(x, dy, mean, scale, ctx.eps)
+        else:
+            dy = dy.contiguous()
+            rows, Cc = x.shape
+            dx = torch.empty_like(x)
+            stats = torch.zeros(3, Cc, dtype=torch.float32, device=x.device)
+            N.check(N.cuda().pbx_data_norm_bwd(N.ptr(x), N.ptr(dy), C.c_int64(rows), Cc, N.ptr(mean), N.ptr(scale),
+                                               C.c_float(ctx.eps), N.ptr(dx), N.ptr(stats[0]), N.ptr(stats[1]),
+                                               N.ptr(stats[2]), N.stream_ptr()))
+            d_size, d_sum, d_sq = stats[0], stats[1], stats[2]
+        if ctx.sink is not None:
+            ctx.sink(d_size, d_sum, d_sq)
+        return dx, None, None, None, None, None
+
+
+class DataNorm(nn.Module):
+    """``y = (x - batch_sum/batch_size) * sqrt(batch_size/batch_square_sum)``.
+
+    The three summaries are *not* trained by the dense optimizer: their "gradients" are
+    the batch statistics and they are updated with a decay
+    (``summary = summary * decay + stat``, data_norm_op.cu:90-110).  With
+    ``sync_stats`` the statistics are first averaged over the data-parallel group
+    (reference: 3 ncclAllReduce calls, data_norm_op.cu:203-231)."""
+
+    def __init__(self, num_features: int, epsilon: float = 1e-4, summary_decay_rate: float = 0.9999999,
+                 sync_stats: bool = False, name: str = "data_norm"):
+        super().__init__()
+        self.name = name
+        self.epsilon = epsilon
+        self.decay = summary_decay_rate
+        self.sync_stats = sync_stats
+        self.register_buffer("batch_size", torch.full((num_features,), 1e4))
+        self.register_buffer("batch_sum", torch.zeros(num_features))
+        self.register_buffer("batch_square_sum", torch.full((num_features,), 1e4))
+        self.reduce_fn = None  # set by the trainer: f(tensor[3, C]) -> averaged in place
+
+    def _apply_stats(self, d_size, d_sum, d_sq):
+        with torch.no_grad():
+            stats = torch.stack([d_size, d_sum, d_sq])
+            if self.sync_stats and self.reduce_fn is not None:
+                stats = self.reduce_fn(stats)
+            self.batch_size.mul_(self.decay).add_(stats[0])
+            self.batch_sum.mul_(self.decay).add_(stats[1])
+            self.batch_square_sum.mul_(self.decay).add_(stats[2])
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        sink = self._apply_stats if self.training else None
+        return _DataNorm.apply(x, self.batch_size, self.batch_sum, self.batch_square_sum, self.epsilon, sink)
+
+
+def data_norm(x, batch_size, batch_sum, batch_square_sum, epsilon: float = 1e-4, stat_sink=None):
+    return _DataNorm.apply(x, batch_size, batch_sum, batch_square_sum, epsilon, stat_sink)
+
+
+# ------------------------------------------------------------------ FM head
+class _FM(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, S, E, wcol, vcol, D):
+        ctx.meta = (S, E, wcol, vcol, D)
+        ctx.save_for_backward(x)
+        B = x.shape[0]
+        out = torch.empty(B, dtype=torch.float32, device=x.device)
+        N.check(N.cuda().pbx_fm_fwd(N.ptr(x), x.stride(0), B, S, E, wcol, vcol, D, N.ptr(out), N.stream_ptr()))
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (x,) = ctx.saved_tensors
+        S, E, wcol, vcol, D = ctx.meta
+        dx = torch.zeros_like(x)
+        N.check(N.cuda().pbx_fm_bwd(N.ptr(x), x.stride(0), N.ptr(g.contiguous()), x.shape[0], S, E, wcol, vcol, D,
+                                    N.ptr(dx), dx.stride(0), 0, N.stream_ptr()))
+        return dx, None, None, None, None, None
+
+
+def fm_interaction(x: torch.Tensor, num_slots: int, slot_width: int, wcol: int, vcol: int, dim: int) -> torch.Tensor:
+    """DeepFM head over pooled slot embeddings ``x`` [B, >= S*E]:
+    ``sum_s w_s + 0.5 * sum_d ((sum_s v_sd)^2 - sum_s v_sd^2)`` -> [B]."""
+    if not x.is_cuda:
+        return R.fm_fwd(x, num_slots, slot_width, wcol, vcol, dim)
+    assert x.stride(1) == 1
+    return _FM.apply(x, num_slots, slot_width, wcol, vcol, dim)
+
+
+# ------------------------------------------------------------------ loss
+class _SigmoidLogLoss(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logit, label):
+        B = logit.numel()
+        logit = logit.contiguous().view(-1)
+        label = label.contiguous().view(-1).float()
+        pred = torch.empty(B, dtype=torch.float32, device=logit.device)
+        loss = torch.zeros((), dtype=torch.float32, device=logit.device)
+        dlogit = torch.empty(B, dtype=torch.float32, device=logit.device)
+        N.check(N.cuda().pbx_sigmoid_logloss(N.ptr(logit), N.ptr(label), B, N.ptr(pred), N.ptr(loss), N.ptr(dlogit),
+                                             C.c_float(1.0 / B), N.stream_ptr()))
+        ctx.save_for_backward(dlogit)
+        ctx.mark_non_differentiable(pred)
+        return loss, pred
+
+    @staticmethod
+    def backward(ctx, gloss, gpred):
+        (dlogit,) = ctx.saved_tensors
+        return dlogit * gloss, None
+
+
+def sigmoid_log_loss(logit: torch.Tensor, label: torch.Tensor):
+    """(mean log-loss, sigmoid(logit)); the logit gradient is produced in the forward kernel."""
+    if not logit.is_cuda:
+        z = logit.view(-1)
+        y = label.view(-1).float()
+        loss = torch.nn.functional.binary_cross_entropy_with_logits(z, y)
+        return loss, torch.sigmoid(z).detach()
+    return _SigmoidLogLoss.apply(logit, label)
+
+
+# ------------------------------------------------------------------ misc CTR utilities
+def row_gather(table: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
+    """Replica-cache gather ``out[i] = table[idx[i]]`` (pull_cache_value, box_wrapper.cu:1210-1224)."""
+    if not table.is_cuda:
+        return table[idx.long()]
+    idx = idx.contiguous().long()
+    out = torch.empty(idx.numel(), table.shape[1], dtype=torch.float32, device=table.device)
+    N.check(N.cuda().pbx_row_gather(N.ptr(table.contiguous()), N.ptr(idx), C.c_int64(idx.numel()), table.shape[1],
+                                    N.ptr(out), N.stream_ptr()))
+    return out

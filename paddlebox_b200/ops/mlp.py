@@ -1,0 +1,228 @@
+"""Dense towers on the tcgen05 GEMM (csrc/cuda/gemm_tcgen05.cu).
+
+``gemm_bf16_tn``  — thin wrapper of the kernel: C = epilogue(alpha * A[M,K] . B[N,K]^T).
+``FusedMLP``      — a whole ReLU tower as ONE autograd node: bf16 operands / fp32
+                    accumulate, bias+ReLU fused in the GEMM epilogue, ReLU-backward mask
+                    fused in the dgrad epilogue, weight gradients accumulated straight into
+                    ``param.grad`` with a split-K GEMM, transposed operand copies produced by
+                    the epilogues (no transpose passes).
+``GroupedMLP``    — E independent towers with the same shapes (MMoE experts; replaces the
+                    reference's ``batch_fc`` BatchedGEMM, operators/batch_fc_op.cu:243).
+
+On CPU (no GPU in the process) the same modules run in plain fp32 PyTorch so that the
+framework's plumbing is testable anywhere; on a GPU box the CUDA path is mandatory.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+import os
+
+import torch
+import torch.nn as nn
+
+from .. import _native as N
+
+
+def _pad8(n: int) -> int:
+    return (n + 7) // 8 * 8
+
+
+def gemm_impl() -> int:
+    """0 = tcgen05 (default), 1 = SIMT cross-check kernel (PBX_GEMM_IMPL=simt)."""
+    return 1 if os.environ.get("PBX_GEMM_IMPL", "tcgen05") == "simt" else 0
+
+
+def gemm_bf16_tn(A: torch.Tensor, B: torch.Tensor, M: int, Nn: int, K: int, *, bias=None, mask=None, out_bf16=None,
+                 out_t=None, out_f32=None, relu=False, accumulate=False, alpha=1.0, splitk=1, block_n=0,
+                 impl=None) -> None:
+    """A: bf16 [>=M, lda], B: bf16 [>=N, ldb] (row strides taken from the tensors)."""
+    assert A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16 and A.is_cuda
+    N.check(N.cuda().pbx_gemm_bf16_tn(
+        N.ptr(A), A.stride(0), N.ptr(B), B.stride(0), M, Nn, K, N.ptr(bias),
+        N.ptr(mask), mask.stride(0) if mask is not None else 0,
+        N.ptr(out_bf16), out_bf16.stride(0) if out_bf16 is not None else 0,
+        N.ptr(out_t), out_t.stride(0) if out_t is not None else 0,
+        N.ptr(out_f32), out_f32.stride(0) if out_f32 is not None else 0,
+        int(relu), int(accumulate), C.c_float(alpha), splitk, block_n,
+        gemm_impl() if impl is None else impl, N.stream_ptr()), "pbx_gemm_bf16_tn")
+
+
+def cast_transpose(x: torch.Tensor, out: torch.Tensor | None, out_t: torch.Tensor | None) -> None:
+    """fp32 [M, K] -> bf16 ``out`` [M, >=K] and/or bf16 ``out_t`` [K, >=M]."""
+    M, K = x.shape
+    N.check(N.cuda().pbx_cast_transpose(N.ptr(x), x.stride(0), M, K, N.ptr(out),
+                                        out.stride(0) if out is not None else 0, N.ptr(out_t),
+                                        out_t.stride(0) if out_t is not None else 0, N.stream_ptr()),
+            "pbx_cast_transpose")
+
+
+def colsum_bf16(x: torch.Tensor, M: int, Nn: int, out: torch.Tensor) -> None:
+    N.check(N.cuda().pbx_colsum_bf16(N.ptr(x), x.stride(0), M, Nn, N.ptr(out), N.stream_ptr()), "pbx_colsum_bf16")
+
+
+class _Workspace:
+    """Per-batch-size activation buffers of one tower (bf16, padded leading dims)."""
+
+    def __init__(self, dims, B, device):
+        bf = torch.bfloat16
+        Bp = _pad8(B)
+        self.B = B
+        # H[l]: [B, dims[l]] activations (l = 0 is the cast input), Ht[l] their transposes
+        self.H = [torch.zeros(B, _pad8(d), dtype=bf, device=device) for d in dims[:-1]]
+        self.Ht = [torch.zeros(d, Bp, dtype=bf, device=device) for d in dims[:-1]]
+        # dZ[l]: grad w.r.t. pre-activation of layer l (1-based), and transposes
+        self.dZ = [torch.zeros(B, _pad8(d), dtype=bf, device=device) for d in dims[1:]]
+        self.dZt = [torch.zeros(d, Bp, dtype=bf, device=device) for d in dims[1:]]
+
+
+class _MLPFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, mod, *params):
+        ctx.mod = mod
+        ctx.x_requires_grad = x.requires_grad
+        return mod._forward_cuda(x, torch.is_grad_enabled() or True)
+
+    @staticmethod
+    def backward(ctx, dout):
+        dx = ctx.mod._backward_cuda(dout.contiguous(), ctx.x_requires_grad)
+        return (dx, None) + (None,) * (2 * len(ctx.mod.weights))
+
+
+class FusedMLP(nn.Module):
+    """ReLU tower ``dims[0] -> dims[1] -> ... -> dims[-1]``; the last layer is linear
+    unless ``final_relu``.  Parameter names follow the reference's convention
+    (``fc_i.w_0`` / ``fc_i.b_0``) so dense checkpoints stay compatible."""
+
+    def __init__(self, dims, final_relu: bool = False, name: str = "fc", seed: int | None = None):
+        super().__init__()
+        self.dims = list(dims)
+        self.final_relu = final_relu
+        self.name = name
+        g = torch.Generator().manual_seed(seed) if seed is not None else None
+        self.weights = nn.ParameterList()
+        self.biases = nn.ParameterList()
+        for k, n in zip(self.dims[:-1], self.dims[1:]):
+            w = torch.empty(n, k)
+            bound = 1.0 / math.sqrt(k)
+            w.uniform_(-bound, bound, generator=g)
+            self.weights.append(nn.Parameter(w))
+            self.biases.append(nn.Parameter(torch.zeros(n)))
+        self._ws: dict[int, _Workspace] = {}
+        self._wb = None          # bf16 weights [N, pad8(K)]
+        self._wbt = None         # bf16 transposed weights [K, pad8(N)]
+        self._dirty = True
+        self._versions = None
+        self._cur = None
+
+    # ---- parameter bookkeeping ------------------------------------------------
+    def named_dense_params(self):
+        for i, (w, b) in enumerate(zip(self.weights, self.biases)):
+            yield f"{self.name}_{i}.w_0", w
+            yield f"{self.name}_{i}.b_0", b
+
+    def mark_weights_dirty(self) -> None:
+        """Call after the dense optimizer changed the fp32 weights outside autograd's
+        version tracking (paddlebox_b200 optimizers do)."""
+        self._dirty = True
+
+    def _refresh_bf16(self) -> None:
+        vers = tuple(w._version for w in self.weights)
+        if not self._dirty and vers == self._versions and self._wb is not None:
+            return
+        dev = self.weights[0].device
+        if self._wb is None:
+            self._wb = [torch.zeros(w.shape[0], _pad8(w.shape[1]), dtype=torch.bfloat16, device=dev)
+                        for w in self.weights]
+            self._wbt = [torch.zeros(w.shape[1], _pad8(w.shape[0]), dtype=torch.bfloat16, device=dev)
+                         for w in self.weights]
+        for w, wb, wbt in zip(self.weights, self._wb, self._wbt):
+            cast_transpose(w.data, wb, wbt)
+        self._dirty = False
+        self._versions = vers
+
+    # ---- execution ------------------------------------------------------------
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if not x.is_cuda:
+            h = x
+            L = len(self.weights)
+            for i, (w, b) in enumerate(zip(self.weights, self.biases)):
+                h = torch.nn.functional.linear(h, w, b)
+                if i < L - 1 or self.final_relu:
+                    h = torch.relu(h)
+            return h
+        return _MLPFn.apply(x, self, *self.weights, *self.biases)
+
+    def _forward_cuda(self, x: torch.Tensor, training: bool) -> torch.Tensor:
+        B = x.shape[0]
+        assert x.shape[1] == self.dims[0] and x.dtype == torch.float32
+        ws = self._ws.get(B)
+        if ws is None:
+            ws = self._ws[B] = _Workspace(self.dims, B, x.device)
+        self._cur = ws
+        self._refresh_bf16()
+        cast_transpose(x.contiguous() if x.stride(1) != 1 else x, ws.H[0], ws.Ht[0])
+        L = len(self.weights)
+        out = torch.empty(B, self.dims[-1], dtype=torch.float32, device=x.device)
+        for l in range(L):
+            last = l == L - 1
+            K, Nn = self.dims[l], self.dims[l + 1]
+            if last:
+                gemm_bf16_tn(ws.H[l], self._wb[l], B, Nn, K, bias=self.biases[l].data, out_f32=out,
+                             relu=self.final_relu)
+            else:
+                gemm_bf16_tn(ws.H[l], self._wb[l], B, Nn, K, bias=self.biases[l].data, out_bf16=ws.H[l + 1],
+                             out_t=ws.Ht[l + 1], relu=True)
+        self._last_out = out if self.final_relu else None
+        return out
+
+    def _backward_cuda(self, dout: torch.Tensor, need_dx: bool):
+        ws = self._cur
+        B = ws.B
+        L = len(self.weights)
+        if self.final_relu:
+            dout = dout * (self._last_out > 0)
+        cast_transpose(dout, ws.dZ[L - 1], ws.dZt[L - 1])
+        dx = None
+        for l in range(L - 1, -1, -1):
+            K, Nn = self.dims[l], self.dims[l + 1]
+            w, b = self.weights[l], self.biases[l]
+            if w.grad is None:
+                w.grad = torch.zeros_like(w.data)
+            if b.grad is None:
+                b.grad = torch.zeros_like(b.data)
+            # wgrad: dW[N, K] += dZ^T[N, B] . (H^T[K, B])^T   (split-K over the batch)
+            splitk = max(1, min(16, B // 512))
+            gemm_bf16_tn(ws.dZt[l], ws.Ht[l], Nn, K, B, out_f32=w.grad, accumulate=True, splitk=splitk)
+            colsum_bf16(ws.dZ[l], B, Nn, b.grad)
+            if l > 0:
+                # dgrad fused with the ReLU mask of the previous activation
+                gemm_bf16_tn(ws.dZ[l], self._wbt[l], B, K, Nn, mask=ws.H[l], out_bf16=ws.dZ[l - 1],
+                             out_t=ws.dZt[l - 1])
+            elif need_dx:
+                dx = torch.empty(B, K, dtype=torch.float32, device=dout.device)
+                gemm_bf16_tn(ws.dZ[0], self._wbt[0], B, K, Nn, out_f32=dx)
+        return dx
+
+
+class GroupedMLP(nn.Module):
+    """``num`` towers of identical shape applied to the same (or per-tower) input; outputs
+    stacked as [num, B, out].  Expert towers of MMoE / the reference's ``batch_fc``."""
+
+    def __init__(self, num: int, dims, final_relu: bool = True, name: str = "expert", seed: int | None = None):
+        super().__init__()
+        self.towers = nn.ModuleList([FusedMLP(dims, final_relu=final_relu, name=f"{name}{i}",
+                                              seed=None if seed is None else seed + i) for i in range(num)])
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        if x.dim() == 3:
+            return torch.stack([t(x[i]) for i, t in enumerate(self.towers)], 0)
+        return torch.stack([t(x) for t in self.towers], 0)
+
+    def mark_weights_dirty(self):
+        for t in self.towers:
+            t.mark_weights_dirty()
+
+    def named_dense_params(self):
+        for t in self.towers:
+            yield from t.named_dense_params()
