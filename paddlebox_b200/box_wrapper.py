@@ -1,0 +1,368 @@
+"""BoxWrapper — the parameter-server façade (reference: ``BoxWrapper`` singleton,
+fleet/box_wrapper.h:377-1012, box_wrapper.cc:129-210, :916-1046, :1201-1324; its Python
+binding box_helper_py.cc:70-160; and the closed ``libbox_ps.so`` behind it).
+
+One instance per process (= per GPU).  It owns
+
+* the HBM shard of the sparse table (``ops.sparse_table.SparseTable``) and the sharded
+  pull/push engine (``parallel.sparse_engine.SparseEngine``) when a GPU is present,
+* the host-memory tier (``host.HostTable``): everything outside the current pass's working
+  set lives there, and it *is* the table in CPU-only mode,
+* the pass lifecycle: ``begin_feed_pass -> (dataset adds keys) -> end_feed_pass ->
+  begin_pass`` stages the pass's keys from the host tier into HBM, ``end_pass`` writes them
+  back (and can save a delta),
+* checkpoints: ``save_base`` (batch model + serving base), ``save_delta``, ``load_model``,
+  ``shrink_table``; text layout ``part-<shard>-<file>`` compatible with pscore's
+  MemorySparseTable,
+* the metric registry (``init_metric`` / ``get_metric_msg``) and the join/update phase.
+"""
+from __future__ import annotations
+
+import json
+import os
+import time
+from typing import Sequence
+
+import numpy as np
+import torch
+
+from . import _native as N
+from .flags import FLAGS
+from .host import HostTable
+from .utils.timer import StageTimers
+
+_MASK64 = np.uint64(0xFFFFFFFFFFFFFFFF)
+
+
+def mix64_np(k: np.ndarray) -> np.ndarray:
+    k = k.astype(np.uint64, copy=True)
+    with np.errstate(over="ignore"):
+        k ^= k >> np.uint64(33)
+        k *= np.uint64(0xff51afd7ed558ccd)
+        k ^= k >> np.uint64(33)
+        k *= np.uint64(0xc4ceb9fe1a85ec53)
+        k ^= k >> np.uint64(33)
+    return k
+
+
+def owner_of(keys: np.ndarray, nranks: int) -> np.ndarray:
+    """Shard of every key; identical to ``pbx_owner_of`` in csrc/cuda/common.cuh."""
+    return ((mix64_np(keys) >> np.uint64(40)) % np.uint64(nranks)).astype(np.int64)
+
+
+def make_day_id(date: str) -> int:
+    """'YYYYMMDD' -> days since epoch (reference make_day_id, box_wrapper.cc:57-70)."""
+    t = time.strptime(date[:8], "%Y%m%d")
+    import calendar
+    return int(calendar.timegm(t) // 86400)
+
+
+class BoxWrapper:
+    _instance: "BoxWrapper | None" = None
+
+    # ---- singleton plumbing (SetInstance / GetInstance) ----------------------------
+    @classmethod
+    def set_instance(cls, embedx_dim: int = 8, expand_embed_dim: int = 0, feature_type: int = 0,
+                     pull_embedx_scale: float = 1.0, **kw) -> "BoxWrapper":
+        if cls._instance is None:
+            cls._instance = cls(embedx_dim, expand_embed_dim, feature_type, pull_embedx_scale, **kw)
+        return cls._instance
+
+    @classmethod
+    def get_instance(cls) -> "BoxWrapper":
+        if cls._instance is None:
+            raise RuntimeError("BoxWrapper.set_instance(...) has not been called")
+        return cls._instance
+
+    @classmethod
+    def reset_instance(cls) -> None:
+        if cls._instance is not None:
+            cls._instance.finalize()
+        cls._instance = None
+
+    def __init__(self, embedx_dim: int = 8, expand_embed_dim: int = 0, feature_type: int = 0,
+                 pull_embedx_scale: float = 1.0, *, optimizer: str = "adagrad", device: torch.device | None = None,
+                 rank: int | None = None, world_size: int | None = None, group=None):
+        """``feature_type``: 0 = fp32 embedx (HeterPS layout), 1 = adam, 2 = shared adam —
+        the closed library's other layouts (int16 quant / nncross / variable) are expressed
+        through ``optimizer`` and ``expand_embed_dim`` here."""
+        self.embedx_dim = embedx_dim
+        self.expand_embed_dim = expand_embed_dim
+        self.feature_type = feature_type
+        self.pull_embedx_scale = pull_embedx_scale
+        self.optimizer = {1: "adam", 2: "shared_adam"}.get(feature_type, optimizer)
+        self.cvm_offset = 3                      # show, clk, embed_w (box_wrapper.h:880)
+        self.hidden = self.cvm_offset + embedx_dim
+        import torch.distributed as dist
+        if rank is None:
+            rank = dist.get_rank(group) if dist.is_available() and dist.is_initialized() else 0
+        if world_size is None:
+            world_size = dist.get_world_size(group) if dist.is_available() and dist.is_initialized() else 1
+        self.rank, self.world_size, self.group = rank, world_size, group
+        self.use_cuda = torch.cuda.is_available() if device is None else device.type == "cuda"
+        self.device = device or (torch.device("cuda", torch.cuda.current_device()) if self.use_cuda
+                                 else torch.device("cpu"))
+        self.config = N.SparseOptConfig()
+        self.host_table: HostTable | None = None
+        self.table = None          # SparseTable (HBM)
+        self.engine = None         # SparseEngine
+        self._phase = 1            # 1 = join, 0 = update (FlipPhase, box_wrapper.h:770-773)
+        self._metrics: dict = {}
+        self._pass_keys: np.ndarray | None = None
+        self._feed_keys: list = []
+        self._day_id = 0
+        self._test_mode = False
+        self._in_pass = False
+        self.timers = StageTimers()
+        self.slot_vector: list = []
+        self.lr_map: dict = {}
+        self._initialized = False
+
+    # ---- initialisation ----------------------------------------------------------------
+    def initialize_gpu_and_load_model(self, conf_file: str | dict | None = None, slot_vector: Sequence[int] = (),
+                                      slot_omit_in_feedpass: Sequence[int] = (), model_path: str = "",
+                                      lr_map: dict | None = None, *, table_capacity: int | None = None,
+                                      max_keys_per_batch: int = 1 << 20) -> None:
+        """``conf_file``: dict or path of a JSON file with the sparse optimizer options
+        (names of ``SparseOptConfig``) plus optional ``table_capacity`` /
+        ``max_keys_per_batch``.  (The closed library reads an opaque conf file;
+        box_wrapper.cc:1201-1242.)"""
+        conf = {}
+        if isinstance(conf_file, dict):
+            conf = dict(conf_file)
+        elif conf_file:
+            with open(conf_file) as f:
+                conf = json.load(f)
+        table_capacity = conf.pop("table_capacity", table_capacity)
+        max_keys_per_batch = conf.pop("max_keys_per_batch", max_keys_per_batch)
+        self.optimizer = conf.pop("optimizer", self.optimizer)
+        self.config = N.SparseOptConfig(**conf)
+        self.slot_vector = list(slot_vector)
+        self.slot_omit_in_feedpass = set(slot_omit_in_feedpass)
+        self.lr_map = dict(lr_map or {})
+        self.max_keys_per_batch = int(max_keys_per_batch)
+        self.host_table = HostTable(self.embedx_dim, self.optimizer, self.config, seed=self.rank)
+        if self.use_cuda:
+            from .ops.sparse_table import SparseTable
+            from .parallel.sparse_engine import SparseEngine
+            cap = int(table_capacity or (1 << 22))
+            self.table = SparseTable(cap, self.embedx_dim, self.optimizer, self.config, seed=self.rank,
+                                     device=self.device.index)
+            cap_pair = 0
+            if self.world_size > 1:
+                cap_pair = int(FLAGS.pbx_sparse_cap_factor * self.max_keys_per_batch / self.world_size) + 1024
+            self.engine = SparseEngine(self.table, self.max_keys_per_batch, self.rank, self.world_size,
+                                       cap=cap_pair, group=self.group)
+        if model_path:
+            self.load_model(model_path)
+        self._initialized = True
+
+    # ---- pass lifecycle ------------------------------------------------------------------
+    def set_date(self, date: str) -> None:
+        self._day_id = make_day_id(date) if not FLAGS.fix_dayid or self._day_id == 0 else self._day_id
+
+    def begin_feed_pass(self, date: str | None = None) -> None:
+        if date:
+            self.set_date(date)
+        self._feed_keys = [np.zeros(1, dtype=np.uint64)]  # key 0 always registered (box_wrapper.h:1107)
+
+    def feed_pass(self, keys) -> None:
+        """Add keys of the coming pass (``PSAgent::AddKeys``)."""
+        k = np.ascontiguousarray(keys.cpu().numpy() if isinstance(keys, torch.Tensor) else keys)
+        self._feed_keys.append(k.view(np.uint64) if k.dtype != np.uint64 else k)
+
+    def end_feed_pass(self) -> None:
+        """Dedup the pass's keys and route every key to the rank that owns it."""
+        t0 = time.time()
+        keys = np.unique(np.concatenate(self._feed_keys)) if self._feed_keys else np.zeros(0, np.uint64)
+        self._feed_keys = []
+        if self.world_size > 1:
+            import torch.distributed as dist
+            own = owner_of(keys, self.world_size)
+            # control-plane exchange of key lists (sizes first, then padded payloads)
+            parts = [keys[own == r] for r in range(self.world_size)]
+            gathered = [None] * self.world_size
+            dist.all_gather_object(gathered, [p.tobytes() for p in parts], group=self.group)
+            mine = [np.frombuffer(g[self.rank], dtype=np.uint64) for g in gathered]
+            keys = np.unique(np.concatenate(mine)) if mine else np.zeros(0, np.uint64)
+        self._pass_keys = keys
+        self.timers.add("feed_pass", time.time() - t0)
+
+    def begin_pass(self) -> None:
+        """Stage the pass working set host tier -> HBM shard."""
+        assert self._initialized, "call initialize_gpu_and_load_model first"
+        t0 = time.time()
+        keys = self._pass_keys if self._pass_keys is not None else np.zeros(0, np.uint64)
+        if self.use_cuda:
+            self.table.clear()
+            # chunked H2D so that staging memory stays bounded (heter_comm_inl.h:671-731)
+            chunk = 1 << 20
+            for i in range(0, keys.size, chunk):
+                ks = keys[i:i + chunk]
+                rows = self.host_table.fetch_rows(ks, create=True)
+                dk = torch.from_numpy(ks.view(np.int64)).to(self.device, non_blocking=False)
+                dr = torch.from_numpy(rows).to(self.device, non_blocking=False)
+                self.table.insert(dk, dr)
+        else:
+            if keys.size:
+                self.host_table.fetch_rows(keys, create=True)  # create missing rows
+        self._in_pass = True
+        self.timers.add("begin_pass", time.time() - t0)
+
+    def end_pass(self, need_save_delta: bool = False, delta_path: str = "") -> None:
+        """Write the HBM working set back to the host tier (``EndPass``)."""
+        t0 = time.time()
+        if self.use_cuda and self._in_pass:
+            torch.cuda.synchronize(self.device)
+            self.engine.check_status()
+            dk, dr = self.table.dump(only_dirty=True, clear_dirty=True)
+            if dk.numel():
+                self.host_table.store_rows(dk.cpu().numpy().view(np.uint64), dr.cpu().numpy(), mark_dirty=True)
+        self._in_pass = False
+        if need_save_delta and delta_path:
+            self.save_delta(delta_path)
+        self.timers.add("end_pass", time.time() - t0)
+
+    # ---- pull / push (single call; autograd wrappers live in ops/pull_box_sparse.py) ----------
+    def pull_sparse(self, keys: torch.Tensor) -> tuple:
+        """Returns (values [U or N, >= hidden], restore int32 [N]); occurrence i's record is
+        ``values[restore[i], :hidden]``."""
+        if self.use_cuda:
+            restore = self.engine.pull(keys)
+            return self.engine.values, restore
+        uk, inv = torch.unique(keys, return_inverse=True)
+        vals = self.host_table.pull(uk.numpy())
+        self._cpu_unique = uk
+        return vals, inv.to(torch.int32)
+
+    def push_sparse_grad(self, keys: torch.Tensor, restore: torch.Tensor, grads: torch.Tensor,
+                         key2slot: torch.Tensor, batch_size: int) -> None:
+        """Per-occurrence gradients [N, hidden] (show, clk counts in the first two columns)."""
+        if self._test_mode:
+            return
+        if self.use_cuda:
+            self.engine.push_keys(restore, grads.contiguous(), key2slot, 2, -float(batch_size))
+            return
+        from .ops import reference as R
+        uk = self._cpu_unique
+        merged = R.merge_push(restore, uk.numel(), grads, key2slot, 2, -float(batch_size))
+        self.host_table.push(uk.numpy(), merged)
+
+    # ---- model save / load -------------------------------------------------------------------
+    def _sync_to_host(self) -> None:
+        if self.use_cuda and self._in_pass:
+            torch.cuda.synchronize(self.device)
+            dk, dr = self.table.dump(only_dirty=True, clear_dirty=True)
+            if dk.numel():
+                self.host_table.store_rows(dk.cpu().numpy().view(np.uint64), dr.cpu().numpy(), mark_dirty=True)
+
+    def save_base(self, batch_model_path: str, xbox_model_path: str = "", date: str = "") -> str:
+        """Full training checkpoint ("batch model", every optimizer state) + serving base
+        ("xbox model")  (box_wrapper.cc:1286-1305)."""
+        self._sync_to_host()
+        n1 = self.host_table.save(batch_model_path, mode=0, shard_base=self.rank, clear_dirty=False)
+        msg = f"batch_model={n1}"
+        if xbox_model_path:
+            n2 = self.host_table.save(xbox_model_path, mode=2, shard_base=self.rank, clear_dirty=False)
+            msg += f" xbox_base={n2}"
+        # a base save resets the delta baseline
+        self.host_table.save(os.path.join(batch_model_path, ".delta_reset"), mode=1, shard_base=self.rank,
+                             clear_dirty=True)
+        import shutil
+        shutil.rmtree(os.path.join(batch_model_path, ".delta_reset"), ignore_errors=True)
+        return msg
+
+    def save_delta(self, xbox_model_path: str) -> str:
+        """Serving-format delta of the keys touched since the last save (box_wrapper.cc:1306-1315)."""
+        self._sync_to_host()
+        n = self.host_table.save(xbox_model_path, mode=1, shard_base=self.rank, clear_dirty=True)
+        return f"xbox_delta={n}"
+
+    def load_model(self, path: str, serving: bool = False) -> int:
+        return self.host_table.load(path, serving=serving)
+
+    def load_ssd2mem(self, date: str = "") -> None:
+        """Host-spill hook; the table is HBM + host-memory resident here."""
+
+    def shrink_table(self, decay: float = 0.98, delete_threshold: float = 0.0,
+                     delete_after_unseen_days: float = 30.0) -> int:
+        self._sync_to_host()
+        return self.host_table.shrink(decay, delete_threshold, delete_after_unseen_days)
+
+    def shrink_resource(self) -> None:
+        if self.use_cuda:
+            torch.cuda.empty_cache()
+
+    def merge_model(self, path: str) -> int:
+        """Merge another checkpoint into the host tier (``MergeModel``): loaded rows replace
+        existing ones."""
+        return self.host_table.load(path)
+
+    def set_test_mode(self, on: bool) -> None:
+        self._test_mode = bool(on)
+        self.host_table.set_test_mode(on)
+        if self.table is not None:
+            self.table.set_test_mode(on)
+
+    def check_need_limit_mem(self) -> bool:
+        if not self.use_cuda:
+            return False
+        free, total = torch.cuda.mem_get_info(self.device)
+        return free < 0.1 * total
+
+    # ---- phases & metrics (box_wrapper.cc:916-1046) --------------------------------------------
+    def phase(self) -> int:
+        return self._phase
+
+    def flip_phase(self) -> None:
+        self._phase = (self._phase + 1) % 2
+
+    def set_phase(self, p: int) -> None:
+        self._phase = p
+
+    def init_metric(self, method: str, name: str, label_varname: str = "label", pred_varname: str = "pred",
+                    cmatch_rank_varname: str = "", mask_varname: str = "", metric_phase: int = 1,
+                    cmatch_rank_group: str = "", ignore_rank: bool = False, bucket_size: int = 1000000,
+                    **kw) -> None:
+        from .metrics import create_metric
+        self._metrics[name] = create_metric(method, name=name, label_varname=label_varname,
+                                            pred_varname=pred_varname, cmatch_rank_varname=cmatch_rank_varname,
+                                            mask_varname=mask_varname, metric_phase=metric_phase,
+                                            cmatch_rank_group=cmatch_rank_group, ignore_rank=ignore_rank,
+                                            bucket_size=bucket_size, device=self.device, **kw)
+
+    def get_metric(self, name: str):
+        return self._metrics[name]
+
+    def get_metric_name_list(self, metric_phase: int = -1) -> list:
+        return [n for n, m in self._metrics.items() if metric_phase < 0 or m.metric_phase == metric_phase]
+
+    def add_metric_data(self, tensors: dict) -> None:
+        """Feed every metric bound to the current phase (AddAucMonitor, boxps_worker.cc:1267-1277)."""
+        for m in self._metrics.values():
+            if m.metric_phase == self._phase:
+                m.add_data(tensors)
+
+    def get_metric_msg(self, name: str) -> list:
+        """[auc, bucket_error, mae, rmse, actual_ctr, predicted_ctr, copc, size]; reduces over
+        the data-parallel group and resets the metric (box_wrapper.cc:1027-1046)."""
+        return self._metrics[name].get_metric_msg(self.group if self.world_size > 1 else None)
+
+    def get_nan_inf_metric_msg(self, name: str) -> list:
+        return self._metrics[name].get_nan_inf_msg()
+
+    # ---- misc ---------------------------------------------------------------------------------
+    def print_sync_timer(self) -> str:
+        """Per-pass stage timers + memory stats (PrintSyncTimer, box_wrapper.cc:1085-1138)."""
+        msg = self.timers.report()
+        if self.use_cuda:
+            msg += f" gpu_mem_used={torch.cuda.memory_allocated(self.device) >> 20}MiB"
+        self.timers.reset()
+        return msg
+
+    def finalize(self) -> None:
+        self.engine = None
+        self.table = None
+        self.host_table = None
+        self._metrics.clear()
+        self._initialized = False

@@ -1,0 +1,500 @@
+"""Datasets: pass-scoped, in-memory SlotRecord data with the reference's Python surface.
+
+Reference: ``DatasetFactory`` / ``InMemoryDataset`` / ``QueueDataset`` / ``BoxPSDataset`` /
+``PadBoxSlotDataset`` / ``InputTableDataset`` (python/paddle/fluid/dataset.py:66-1497; fleet
+flavour python/paddle/distributed/fleet/dataset/dataset.py) over the C++ datasets
+(framework/data_set.cc) and feeds (framework/data_feed.cc).  Here the C++ side is
+``csrc/host/dataset.cc``; this module keeps the setter names (``set_use_var``,
+``set_batch_size``, ``set_thread``, ``set_filelist``, ``set_pipe_command``,
+``set_parse_ins_id``, ``set_date``, ``preload_into_memory`` ...) so a user script ports by
+changing the import.
+
+Batches come out as ``SlotBatch`` objects (``ops/pull_box_sparse.py``).  On a GPU the host
+packs a batch record-major into ONE pinned staging buffer, issues ONE H2D copy and the
+``batch_build`` kernel produces the slot-major layout (csrc/cuda/batch_build.cu); the next
+batch is packed by a background thread while the current one trains.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import threading
+import queue
+from dataclasses import dataclass, field
+from typing import Iterator, Sequence
+
+import numpy as np
+import torch
+
+from . import _native as N
+from .box_wrapper import BoxWrapper
+from .flags import FLAGS
+from .host import NativeDataset
+from .ops.pull_box_sparse import SlotBatch
+from .utils import monitor
+
+
+@dataclass
+class SlotVar:
+    """Stand-in for the reference's program ``Variable`` passed to ``set_use_var``:
+    int64 + lod_level 1 = sparse id slot, float32 + lod_level 0 = dense slot of ``shape[-1]``
+    values (dataset.py:270-302)."""
+    name: str
+    dtype: str = "int64"
+    lod_level: int = 1
+    shape: tuple = (-1, 1)
+    is_used: bool = True
+
+    def desc(self) -> dict:
+        is_float = self.dtype in ("float32", "float")
+        dim = int(self.shape[-1]) if self.lod_level == 0 and len(self.shape) else 1
+        return {"name": self.name, "type": 1 if is_float else 0, "is_dense": int(self.lod_level == 0),
+                "is_used": int(self.is_used), "dim": max(dim, 1)}
+
+
+def sparse_slot(name: str) -> SlotVar:
+    return SlotVar(name, "int64", 1, (-1, 1))
+
+
+def dense_slot(name: str, dim: int = 1) -> SlotVar:
+    return SlotVar(name, "float32", 0, (-1, dim))
+
+
+class DatasetBase:
+    def __init__(self):
+        self._native = NativeDataset()
+        self.use_vars: list = []
+        self.all_slots: list = []
+        self.batch_size = 1
+        self.thread_num = 1
+        self.filelist: list = []
+        self.pipe_command = "cat"
+        self.fs_name = self.fs_ugi = ""
+        self.download_cmd = "cat"
+        self.trainer_num = 1
+        self._prepared_workers = 0
+        self._device = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() \
+            else torch.device("cpu")
+
+    # ---- configuration (same names as the reference) ------------------------------------
+    def init(self, batch_size=1, thread_num=1, use_var=(), pipe_command="cat", input_type=0, fs_name="",
+             fs_ugi="", download_cmd="cat", **kw):
+        self.set_batch_size(batch_size)
+        self.set_thread(thread_num)
+        if use_var:
+            self.set_use_var(use_var)
+        self.set_pipe_command(pipe_command)
+        self.set_hdfs_config(fs_name, fs_ugi)
+        self.set_download_cmd(download_cmd)
+        for k, v in kw.items():
+            setter = getattr(self, "set_" + k, None)
+            if setter is None:
+                raise TypeError(f"unknown dataset option {k!r}")
+            setter(v)
+
+    def set_use_var(self, var_list: Sequence[SlotVar], all_slots: Sequence[SlotVar] | None = None):
+        """``var_list`` are the variables the program consumes; ``all_slots`` (optional) is the
+        full slot order of the data files — slots not in ``var_list`` are parsed over
+        (``is_used = False``)."""
+        self.use_vars = list(var_list)
+        used = {v.name for v in var_list}
+        slots = list(all_slots) if all_slots is not None else list(var_list)
+        self.all_slots = [SlotVar(s.name, s.dtype, s.lod_level, s.shape, s.name in used) for s in slots]
+        self._native.set_slots([s.desc() for s in self.all_slots])
+
+    def set_batch_size(self, batch_size: int):
+        self.batch_size = int(batch_size)
+        self._native.set("batch_size", self.batch_size)
+
+    def set_thread(self, thread_num: int):
+        self.thread_num = int(thread_num)
+        self._native.set("thread_num", self.thread_num)
+
+    def set_filelist(self, filelist: Sequence[str]):
+        self.filelist = list(filelist)
+        self._native.set_filelist(self.filelist)
+
+    def set_pipe_command(self, pipe_command: str):
+        """A shell filter every file is piped through, or the path of a parser plugin ``.so``
+        (reference: ``pipe_command`` may name a parser library, data_feed.cc:3604-3670)."""
+        self.pipe_command = pipe_command
+        if pipe_command.endswith(".so"):
+            self._native.set("parser_plugin", pipe_command)
+            self._native.set("pipe_command", "cat")
+        else:
+            self._native.set("pipe_command", pipe_command)
+
+    def set_hdfs_config(self, fs_name: str, fs_ugi: str):
+        self.fs_name, self.fs_ugi = fs_name, fs_ugi
+
+    def set_download_cmd(self, download_cmd: str):
+        self.download_cmd = download_cmd
+
+    def set_trainer_num(self, n: int):
+        self.trainer_num = n
+
+    def desc(self) -> str:
+        """Text description of the feed configuration (``DataFeedDesc``, data_feed.proto:45-57)."""
+        lines = [f"name: \"{type(self).__name__}\"", f"batch_size: {self.batch_size}",
+                 f"pipe_command: \"{self.pipe_command}\"", f"thread_num: {self.thread_num}", "multi_slot_desc {"]
+        for s in self.all_slots:
+            d = s.desc()
+            lines.append(f"  slots {{ name: \"{d['name']}\" type: \"{'float' if d['type'] else 'uint64'}\" "
+                         f"is_dense: {bool(d['is_dense'])} is_used: {bool(d['is_used'])} shape: {d['dim']} }}")
+        lines.append("}")
+        return "\n".join(lines)
+
+    # ---- geometry ---------------------------------------------------------------------------
+    @property
+    def num_sparse_slots(self) -> int:
+        return self._native.n_sparse()
+
+    @property
+    def dense_dim(self) -> int:
+        return self._native.dense_dim()
+
+
+class InMemoryDataset(DatasetBase):
+    """Loads a pass into host memory, shuffles, deals equal batch counts to the workers."""
+
+    def __init__(self):
+        super().__init__()
+        self.parse_ins_id = False
+        self.parse_logkey = False
+        self.merge_by_lineid = False
+        self.fleet_send_batch_size = 1024
+        self.queue_num = None
+        self.fea_eval = False
+        self._shuffle_seed = 0
+        self._worker = 0
+
+    # setters (dataset.py:372-1105) -----------------------------------------------------------
+    def set_parse_ins_id(self, v: bool):
+        self.parse_ins_id = bool(v)
+        self._native.set("parse_ins_id", int(v))
+
+    def set_parse_logkey(self, v: bool):
+        self.parse_logkey = bool(v)
+        self._native.set("parse_logkey", int(v))
+
+    def set_parse_content(self, v: bool):
+        self.parse_content = bool(v)
+
+    def set_merge_by_sid(self, v: bool):
+        self.merge_by_sid = bool(v)
+
+    def set_enable_pv_merge(self, v: bool):
+        self._native.set("enable_pv_merge", int(v))
+
+    def set_merge_by_lineid(self, merge_size: int = 2):
+        self.merge_by_lineid = True
+        self.merge_size = merge_size
+
+    def set_sample_rate(self, rate: float):
+        self._native.set("sample_rate", float(rate))
+
+    def set_queue_num(self, n: int):
+        self.queue_num = n
+
+    def set_fleet_send_batch_size(self, n: int = 1024):
+        self.fleet_send_batch_size = n
+
+    def set_fleet_send_sleep_seconds(self, s: int = 0):
+        self.fleet_send_sleep_seconds = s
+
+    def set_fea_eval(self, record_candidate_size: int, fea_eval: bool = True):
+        self.fea_eval = fea_eval
+        self.candidate_size = record_candidate_size
+
+    def set_rank_offset(self, name: str):
+        self.rank_offset_name = name
+
+    def set_pv_batch_size(self, n: int):
+        self.pv_batch_size = n
+
+    def set_ads_offset(self, name: str):
+        self.ads_offset_name = name
+
+    def set_merge_thread_num(self, n: int):
+        self._native.set("merge_thread_num", int(n))
+
+    def set_shuffle_seed(self, seed: int):
+        self._shuffle_seed = int(seed)
+
+    def set_rank_world(self, rank: int, world: int):
+        """Files are dealt round-robin over nodes (SetFileList, data_set.cc:1963-1975)."""
+        self._native.set("rank", rank)
+        self._native.set("world", world)
+
+    # pass data ---------------------------------------------------------------------------------
+    def load_into_memory(self):
+        self._native.load_into_memory()
+        monitor.stat_set("STAT_total_feasign_num_in_mem", self._native.total_feasigns())
+
+    def preload_into_memory(self, thread_num: int | None = None):
+        if thread_num:
+            self.set_thread(thread_num)
+        self._native.preload_into_memory()
+
+    def wait_preload_done(self):
+        self._native.wait_preload_done()
+        monitor.stat_set("STAT_total_feasign_num_in_mem", self._native.total_feasigns())
+
+    def release_memory(self):
+        self._native.release_memory()
+        self._prepared_workers = 0
+
+    def local_shuffle(self):
+        self._native.local_shuffle(self._shuffle_seed)
+
+    def global_shuffle(self, fleet=None, thread_num: int = 12):
+        """Single-node scope: a global shuffle is a local one; with several nodes records are
+        re-partitioned by ``parallel.shuffle.global_shuffle_records``."""
+        self._native.local_shuffle(self._shuffle_seed)
+
+    def slots_shuffle(self, slots: Sequence[str]):
+        """Permute the feasigns of ``slots`` across instances (AUC runner feature evaluation)."""
+        names = [s.name for s in self.all_slots]
+        self._native.slots_shuffle([names.index(s) for s in slots], self._shuffle_seed + 1)
+
+    def get_memory_data_size(self, fleet=None) -> int:
+        return self._native.num_records()
+
+    def get_shuffle_data_size(self, fleet=None) -> int:
+        return self._native.num_records()
+
+    def get_pv_data_size(self) -> int:
+        return self._native.num_records()
+
+    def unique_keys(self) -> np.ndarray:
+        return self._native.unique_keys()
+
+    def stats(self) -> str:
+        return self._native.stats()
+
+    # preload_into_disk / archive mode (data_set.cc:2092-2217) ---------------------------------
+    def set_archivefile(self, path: str):
+        self._archive = path
+
+    def preload_into_disk(self, path: str | None = None):
+        self._native.load_into_memory()
+        self._native.save_archive(path or self._archive)
+        self._native.release_memory()
+
+    def load_into_disk(self, path: str | None = None):
+        self.preload_into_disk(path)
+
+    def wait_load_disk_done(self):
+        self._native.load_archive(self._archive)
+
+    # training iteration ---------------------------------------------------------------------------
+    def prepare_train(self, num_workers: int = 1, worker: int = 0, shuffle: bool | None = None,
+                      min_batches: int = 0):
+        """Shuffle + deal batches so that every worker (= GPU) gets the same number
+        (``PrepareTrain``, data_set.cc:2692-2823)."""
+        if shuffle is None:
+            shuffle = not FLAGS.padbox_disable_ins_shuffle
+        self._native.prepare_train(num_workers, shuffle, self._shuffle_seed, min_batches)
+        self._prepared_workers = num_workers
+        self._worker = worker
+
+    def dynamic_adjust_readers_num(self, thread_num: int):
+        self.prepare_train(thread_num)
+
+    def num_batches(self, worker: int | None = None) -> int:
+        return self._native.num_batches(self._worker if worker is None else worker)
+
+    def batches(self, worker: int | None = None, device: torch.device | None = None, prefetch: int = 2,
+                with_ins_id: bool = False) -> Iterator[SlotBatch]:
+        """Iterate this worker's batches as ``SlotBatch`` (double-buffered H2D on GPU)."""
+        if self._prepared_workers == 0:
+            self.prepare_train(1)
+        w = self._worker if worker is None else worker
+        device = device or self._device
+        loader = _BatchLoader(self._native, w, device, prefetch, with_ins_id)
+        return iter(loader)
+
+
+class QueueDataset(InMemoryDataset):
+    """Streaming flavour (reference ``QueueDataset``: no shuffle).  Here it loads file by file
+    and never shuffles or collects keys."""
+
+    def __init__(self):
+        super().__init__()
+        self._native.set("collect_keys", 0)
+
+    def local_shuffle(self):
+        raise NotImplementedError("QueueDataset does not support local shuffle")
+
+    def global_shuffle(self, fleet=None, thread_num=12):
+        raise NotImplementedError("QueueDataset does not support global shuffle")
+
+    def prepare_train(self, num_workers=1, worker=0, shuffle=None, min_batches=0):
+        super().prepare_train(num_workers, worker, False, min_batches)
+
+
+class BoxPSDataset(InMemoryDataset):
+    """Dataset bound to the BoxWrapper pass lifecycle (``BoxHelper``, box_wrapper.h:1043-1295):
+    ``load_into_memory`` = BeginFeedPass -> read + collect keys -> EndFeedPass."""
+
+    def __init__(self):
+        super().__init__()
+        self._date = ""
+
+    @property
+    def boxps(self) -> BoxWrapper:
+        return BoxWrapper.get_instance()
+
+    def set_date(self, date: str):
+        self._date = str(date)
+        self.boxps.set_date(self._date)
+
+    def begin_pass(self):
+        self.boxps.begin_pass()
+
+    def end_pass(self, need_save_delta: bool = False, delta_path: str = ""):
+        self.boxps.end_pass(need_save_delta, delta_path)
+
+    def _feed_keys(self):
+        self.boxps.begin_feed_pass(self._date or None)
+        self.boxps.feed_pass(self._native.unique_keys())
+        self.boxps.end_feed_pass()
+
+    def load_into_memory(self):
+        super().load_into_memory()
+        self._feed_keys()
+
+    def wait_preload_done(self):
+        super().wait_preload_done()
+        self._feed_keys()
+
+    def wait_feed_pass_done(self):
+        self.wait_preload_done()
+
+
+class PadBoxSlotDataset(BoxPSDataset):
+    """SlotRecord dataset of PaddleBox (``PadBoxSlotDataset``, dataset.py:1363-1497)."""
+
+    def disable_polling(self, v: bool = True):
+        FLAGS.padbox_dataset_disable_polling = v
+
+    def disable_shuffle(self, v: bool = True):
+        FLAGS.padbox_dataset_disable_shuffle = v
+
+
+class InputTableDataset(PadBoxSlotDataset):
+    """Dataset whose instances carry string keys of an ``InputTable`` (replica side table,
+    data_set.cc:2830-2858); index files are parsed like data files."""
+
+    def set_index_filelist(self, filelist: Sequence[str]):
+        self.index_filelist = list(filelist)
+
+
+class DatasetFactory:
+    """``DatasetFactory().create_dataset("PadBoxSlotDataset")`` (dataset.py:30-63)."""
+    _KINDS = {"InMemoryDataset": InMemoryDataset, "QueueDataset": QueueDataset, "BoxPSDataset": BoxPSDataset,
+              "PadBoxSlotDataset": PadBoxSlotDataset, "InputTableDataset": InputTableDataset,
+              "SlotRecordDataset": InMemoryDataset, "MultiSlotDataset": InMemoryDataset}
+
+    def create_dataset(self, datafeed_class: str = "QueueDataset"):
+        try:
+            return self._KINDS[datafeed_class]()
+        except KeyError:
+            raise ValueError(f"datafeed class {datafeed_class} does not exist") from None
+
+
+# --------------------------------------------------------------------------------------------
+class _PinnedStage:
+    """One pinned staging buffer: [keys u64 | offsets i32 | dense f32]."""
+
+    def __init__(self, key_cap: int, off_cap: int, dense_cap: int, pinned: bool):
+        self.key_cap, self.off_cap, self.dense_cap = key_cap, off_cap, dense_cap
+        nbytes = key_cap * 8 + off_cap * 4 + dense_cap * 4
+        self.buf = torch.empty(nbytes, dtype=torch.uint8, pin_memory=pinned)
+        base = self.buf.data_ptr()
+        self.keys_ptr = base
+        self.off_ptr = base + key_cap * 8
+        self.dense_ptr = self.off_ptr + off_cap * 4
+
+    def views(self, n_keys: int, n_off: int, n_dense: int):
+        k = self.buf[:n_keys * 8].view(torch.int64)
+        o = self.buf[self.key_cap * 8:self.key_cap * 8 + n_off * 4].view(torch.int32)
+        d = self.buf[self.key_cap * 8 + self.off_cap * 4:self.key_cap * 8 + self.off_cap * 4 + n_dense * 4] \
+            .view(torch.float32)
+        return k, o, d
+
+
+class _BatchLoader:
+    def __init__(self, native: NativeDataset, worker: int, device: torch.device, prefetch: int, with_ins_id: bool):
+        self.native, self.worker, self.device = native, worker, device
+        self.S = native.n_sparse()
+        self.Dd = native.dense_dim()
+        self.nb = native.num_batches(worker)
+        self.with_ins_id = with_ins_id
+        self.cuda = device.type == "cuda"
+        self.q: "queue.Queue" = queue.Queue(maxsize=max(1, prefetch))
+        self.stages: list = []
+        self.free: "queue.Queue" = queue.Queue()
+        self.thread = threading.Thread(target=self._produce, daemon=True)
+        self.prefetch = max(1, prefetch)
+
+    def _stage_for(self, B: int, n: int) -> _PinnedStage:
+        try:
+            st = self.free.get_nowait()
+            if st.key_cap >= n and st.off_cap >= B * (self.S + 1) + 1 and st.dense_cap >= B * self.Dd:
+                return st
+        except queue.Empty:
+            pass
+        if len(self.stages) >= self.prefetch + 2:
+            st = self.free.get()
+            if st.key_cap >= n and st.off_cap >= B * (self.S + 1) + 1 and st.dense_cap >= B * self.Dd:
+                return st
+        st = _PinnedStage(int(n * 1.25) + 1024, B * (self.S + 1) + self.S + 2, max(B * self.Dd, 1), self.cuda)
+        self.stages.append(st)
+        return st
+
+    def _produce(self):
+        try:
+            for b in range(self.nb):
+                B, n = self.native.batch_shape(self.worker, b)
+                st = self._stage_for(B, n)
+                # GPU: record-major (batch_build transposes on the device); CPU: slot-major directly
+                self.native.pack_batch(self.worker, b, st.keys_ptr, st.off_ptr, st.dense_ptr, not self.cuda)
+                ids = self.native.batch_ins_ids(self.worker, b) if self.with_ins_id else None
+                self.q.put((b, B, n, st, ids))
+        finally:
+            self.q.put(None)
+
+    def __iter__(self):
+        self.thread.start()
+        S, Dd = self.S, self.Dd
+        while True:
+            item = self.q.get()
+            if item is None:
+                return
+            b, B, n, st, ids = item
+            if self.cuda:
+                n_off = B * (S + 1)
+                k, o, d = st.views(n, n_off, B * Dd)
+                # ONE H2D of the staging bytes actually used would need one contiguous range;
+                # the three regions are contiguous per kind, so copy them back to back
+                dk = k.to(self.device, non_blocking=True)
+                do = o.to(self.device, non_blocking=True)
+                dd = d.to(self.device, non_blocking=True).view(B, Dd) if Dd else None
+                keys = torch.empty(max(n, 1), dtype=torch.int64, device=self.device)
+                lod = torch.empty(S * B + 1, dtype=torch.int32, device=self.device)
+                scratch = torch.empty(1024, dtype=torch.int32, device=self.device)
+                N.check(N.cuda().pbx_batch_build(N.ptr(dk), N.ptr(do), B, S, N.ptr(keys), N.ptr(lod),
+                                                 N.ptr(scratch), N.stream_ptr()), "pbx_batch_build")
+                ev = torch.cuda.Event()
+                ev.record()
+                batch = SlotBatch(keys[:n], lod, B, S, dd, n_keys=n, ins_ids=ids)
+                batch._keepalive = (dk, do, scratch)
+                yield batch
+                ev.synchronize()   # staging buffer may be reused once its copies are done
+                self.free.put(st)
+            else:
+                k, o, d = st.views(n, S * B + 1, B * Dd)
+                batch = SlotBatch(k.clone(), o.clone(), B, S, d.clone().view(B, Dd) if Dd else None, n_keys=n,
+                                  ins_ids=ids)
+                self.free.put(st)
+                yield batch

@@ -1,0 +1,268 @@
+"""AUC-family metrics (reference: ``MetricMsg`` and its subclasses,
+fleet/box_wrapper.h:265-376, box_wrapper.cc:372-886; ``BasicAucCalculator``,
+fleet/metrics.cc:38-409, :501-587; registry ``InitMetric`` box_wrapper.cc:916-1025).
+
+Each metric owns a C++ ``HostAuc`` calculator (csrc/host/metrics.cc).  CUDA predictions are
+bucketed *on the device* by ``pbx_auc_bucket`` (csrc/cuda/dense_ops.cu) into a
+``[2, buckets]`` fp64 table that is merged into the calculator only when the metric is
+read — the reference copies pred/label to the host and buckets under a mutex every batch
+(metrics.cc:115-136).  ``get_metric_msg`` reduces the tables over the data-parallel group
+(reference: MPI / Gloo allreduce, metrics.cc:284-332) and returns
+``[auc, bucket_error, mae, rmse, actual_ctr, predicted_ctr, copc, size]``.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _native as N
+from .host import HostAuc
+
+
+def parse_cmatch_rank(x: torch.Tensor):
+    """High 32 bits = cmatch, low 8 bits = rank (box_wrapper.h:364-368)."""
+    x = x.to(torch.int64)
+    return (x >> 32) & 0xFFFFFFFF, x & 0xFF
+
+
+class MetricMsg:
+    def __init__(self, name="", label_varname="label", pred_varname="pred", metric_phase=1, bucket_size=1000000,
+                 device=None, float_label=False, **_):
+        self.name = name
+        self.label_varname, self.pred_varname = label_varname, pred_varname
+        self.metric_phase = metric_phase
+        self.bucket_size = bucket_size
+        self.float_label = float_label
+        self.calc = HostAuc(bucket_size)
+        self.device = device
+        self._dev_table = None
+        self._dev_sums = None
+
+    # ---- data intake -------------------------------------------------------------
+    def _add(self, pred: torch.Tensor, label: torch.Tensor, mask: torch.Tensor | None = None):
+        pred = pred.detach().reshape(-1).float()
+        label = label.detach().reshape(-1).float()
+        if mask is not None:
+            mask = mask.detach().reshape(-1).float()
+        if pred.is_cuda and not self.float_label:
+            if self._dev_table is None:
+                self._dev_table = torch.zeros(2, self.bucket_size, dtype=torch.float64, device=pred.device)
+                self._dev_sums = torch.zeros(5, dtype=torch.float64, device=pred.device)
+            N.check(N.cuda().pbx_auc_bucket(N.ptr(pred.contiguous()), N.ptr(label.contiguous()),
+                                            N.ptr(mask.contiguous()) if mask is not None else None,
+                                            C.c_int64(pred.numel()), self.bucket_size, N.ptr(self._dev_table),
+                                            N.ptr(self._dev_sums), N.stream_ptr()), "pbx_auc_bucket")
+        else:
+            self.calc.add(pred.cpu().numpy(), label.cpu().numpy(), None if mask is None else mask.cpu().numpy(),
+                          self.float_label)
+
+    def add_data(self, tensors: dict):
+        self._add(tensors[self.pred_varname], tensors[self.label_varname])
+
+    # ---- read-out ------------------------------------------------------------------
+    def _flush_device(self):
+        if self._dev_table is not None:
+            self.calc.merge_tables(self._dev_table.cpu().numpy(), self._dev_sums.cpu().numpy())
+            self._dev_table.zero_()
+            self._dev_sums.zero_()
+
+    def _reduce(self, group):
+        if group is None:
+            return
+        import torch.distributed as dist
+        t, s = self.calc.export_state()
+        buf = torch.from_numpy(np.concatenate([t.reshape(-1), s]))
+        if dist.get_backend(group) == "nccl":
+            buf = buf.cuda()
+        dist.all_reduce(buf, group=group)
+        buf = buf.cpu().numpy()
+        self.calc.import_state(buf[:2 * self.bucket_size].reshape(2, -1), buf[2 * self.bucket_size:])
+
+    def get_metric_msg(self, group=None) -> list:
+        self._flush_device()
+        self._reduce(group)
+        out = self.calc.compute()
+        self.calc.reset()
+        return out
+
+    def get_nan_inf_msg(self) -> list:
+        self._flush_device()
+        return list(self.calc.nan_inf())
+
+
+class MaskMetricMsg(MetricMsg):
+    """Only rows whose mask is non-zero count (MaskAucCalculator)."""
+
+    def __init__(self, mask_varname="mask", **kw):
+        super().__init__(**kw)
+        self.mask_varname = mask_varname
+
+    def add_data(self, tensors):
+        self._add(tensors[self.pred_varname], tensors[self.label_varname], tensors[self.mask_varname])
+
+
+class MultiMaskMetricMsg(MetricMsg):
+    """Rows where every listed mask variable equals its listed value (MultiMaskAucCalculator)."""
+
+    def __init__(self, mask_varname="", mask_varvalue_list="", **kw):
+        super().__init__(**kw)
+        self.mask_names = mask_varname.split()
+        self.mask_values = [int(v) for v in str(mask_varvalue_list).split()]
+        assert len(self.mask_names) == len(self.mask_values)
+
+    def add_data(self, tensors):
+        keep = None
+        for n, v in zip(self.mask_names, self.mask_values):
+            m = tensors[n].reshape(-1) == v
+            keep = m if keep is None else keep & m
+        self._add(tensors[self.pred_varname], tensors[self.label_varname], keep.float())
+
+
+class CmatchRankMetricMsg(MetricMsg):
+    """Rows whose (cmatch, rank) is in ``cmatch_rank_group`` ("c_r c_r ..."; with
+    ``ignore_rank`` only cmatch is compared) (CmatchRankAucCalculator)."""
+
+    def __init__(self, cmatch_rank_group="", cmatch_rank_varname="cmatch_rank", ignore_rank=False, **kw):
+        super().__init__(**kw)
+        self.cmatch_rank_varname = cmatch_rank_varname
+        self.ignore_rank = ignore_rank
+        self.pairs = []
+        for tok in cmatch_rank_group.split():
+            if ignore_rank:
+                self.pairs.append((int(tok), 0))
+            else:
+                c, r = tok.split("_")
+                self.pairs.append((int(c), int(r)))
+
+    def _select(self, tensors):
+        cm, rk = parse_cmatch_rank(tensors[self.cmatch_rank_varname].reshape(-1))
+        keep = torch.zeros_like(cm, dtype=torch.bool)
+        for c, r in self.pairs:
+            keep |= (cm == c) if self.ignore_rank else ((cm == c) & (rk == r))
+        return keep
+
+    def add_data(self, tensors):
+        self._add(tensors[self.pred_varname], tensors[self.label_varname], self._select(tensors).float())
+
+
+class CmatchRankMaskMetricMsg(CmatchRankMetricMsg):
+    def __init__(self, mask_varname="mask", **kw):
+        super().__init__(**kw)
+        self.mask_varname = mask_varname
+
+    def add_data(self, tensors):
+        keep = self._select(tensors) & (tensors[self.mask_varname].reshape(-1) != 0)
+        self._add(tensors[self.pred_varname], tensors[self.label_varname], keep.float())
+
+
+class MultiTaskMetricMsg(MetricMsg):
+    """One prediction variable per (cmatch, rank) pair; a row feeds the prediction whose pair
+    it matches (MultiTaskAucCalculator, box_wrapper.cc:372-455)."""
+
+    def __init__(self, cmatch_rank_group="", cmatch_rank_varname="cmatch_rank", **kw):
+        super().__init__(**kw)
+        self.cmatch_rank_varname = cmatch_rank_varname
+        self.pairs = [tuple(int(v) for v in tok.split("_")) for tok in cmatch_rank_group.split()]
+        self.pred_names = self.pred_varname.split()
+        assert len(self.pairs) == len(self.pred_names), "cmatch_rank group and pred list sizes differ"
+
+    def add_data(self, tensors):
+        cm, rk = parse_cmatch_rank(tensors[self.cmatch_rank_varname].reshape(-1))
+        label = tensors[self.label_varname]
+        for (c, r), pn in zip(self.pairs, self.pred_names):
+            self._add(tensors[pn], label, ((cm == c) & (rk == r)).float())
+
+
+class FloatMaskMetricMsg(MaskMetricMsg):
+    """Float labels in [0, 1] split fractionally between the two tables (FloatMaskAucCalculator)."""
+
+    def __init__(self, **kw):
+        super().__init__(float_label=True, **kw)
+
+
+class ContinueMaskMetricMsg(MaskMetricMsg):
+    """Regression-style metric on masked rows: only mae / rmse / mean prediction / mean label
+    are meaningful (ContinueMaskCalculator)."""
+
+    def __init__(self, **kw):
+        super().__init__(float_label=True, **kw)
+
+    def get_metric_msg(self, group=None):
+        self._flush_device()
+        self._reduce(group)
+        t, s = self.calc.export_state()
+        n = max(s[4], 1.0)
+        self.calc.reset()
+        # [mae, rmse, predicted mean, actual mean, size]
+        return [s[0] / n, float(np.sqrt(s[1] / n)), s[2] / n, s[3] / n, s[4]]
+
+
+class WuAucMetricMsg(MetricMsg):
+    """Per-user AUC: uauc (mean over users) and wuauc (instance-weighted)
+    (metrics.cc:501-587)."""
+
+    def __init__(self, uid_varname="uid", **kw):
+        super().__init__(**kw)
+        self.uid_varname = uid_varname
+
+    def add_data(self, tensors):
+        self.calc.add_uid(tensors[self.pred_varname].detach().float().cpu().numpy(),
+                          tensors[self.label_varname].detach().float().cpu().numpy(),
+                          tensors[self.uid_varname].detach().cpu().numpy())
+
+    def get_metric_msg(self, group=None):
+        out = self.calc.compute_wuauc()   # [uauc, wuauc, user_cnt, size]
+        self.calc.reset()
+        return out
+
+
+class NanInfMetricMsg(MetricMsg):
+    """Counts NaN / Inf predictions (NanInfCalculator, box_wrapper.cc:853-886)."""
+
+    def __init__(self, **kw):
+        super().__init__(**kw)
+        self.nan = 0
+        self.inf = 0
+        self.total = 0
+
+    def add_data(self, tensors):
+        p = tensors[self.pred_varname].detach().reshape(-1)
+        self.nan += int(torch.isnan(p).sum())
+        self.inf += int(torch.isinf(p).sum())
+        self.total += p.numel()
+
+    def get_nan_inf_msg(self):
+        out = [self.nan, self.inf, self.total]
+        self.nan = self.inf = self.total = 0
+        return out
+
+    def get_metric_msg(self, group=None):
+        return self.get_nan_inf_msg()
+
+
+_REGISTRY = {
+    "AucCalculator": MetricMsg,
+    "MultiTaskAucCalculator": MultiTaskMetricMsg,
+    "CmatchRankAucCalculator": CmatchRankMetricMsg,
+    "MaskAucCalculator": MaskMetricMsg,
+    "MultiMaskAucCalculator": MultiMaskMetricMsg,
+    "CmatchRankMaskAucCalculator": CmatchRankMaskMetricMsg,
+    "FloatMaskAucCalculator": FloatMaskMetricMsg,
+    "ContinueMaskCalculator": ContinueMaskMetricMsg,
+    "WuAucCalculator": WuAucMetricMsg,
+    "NanInfCalculator": NanInfMetricMsg,
+}
+
+
+def create_metric(method: str, **kw) -> MetricMsg:
+    if method not in _REGISTRY:
+        raise ValueError(f"unsupported metric {method!r}; supported: {sorted(_REGISTRY)}")
+    cls = _REGISTRY[method]
+    kw = {k: v for k, v in kw.items() if v not in (None,)}
+    # drop empty optional names so that subclass defaults apply
+    for opt in ("mask_varname", "cmatch_rank_varname", "cmatch_rank_group"):
+        if kw.get(opt, None) == "":
+            kw.pop(opt)
+    return cls(**kw)

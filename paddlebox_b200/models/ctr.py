@@ -1,0 +1,171 @@
+"""CTR model families on top of the sparse ops and the tcgen05 towers.
+
+The reference ships no model code (the user script builds a static Program from
+``_pull_box_sparse`` + ``fused_seqpool_cvm`` + fc towers); BASELINE.json names
+the families the framework must run: CTR-DNN, Wide&Deep, DeepFM, MMoE.  All of them share
+the sparse front end:
+
+    ids --pull_box_sparse--> [show, clk, embed_w, embedx] --fused_seqpool_cvm--> [B, S*(3+D)]
+
+with per-slot columns ``[log(show+1), log(clk+1)-log(show+1), embed_w, embedx_0..D-1]``.
+
+Batch convention: ``batch.dense`` is ``[B, n_labels + dense_dim]`` — label column(s) first.
+``forward`` returns ``(loss, {"pred": ..., "label": ...})``.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from ..box_wrapper import BoxWrapper
+from ..ops import functional as F
+from ..ops.mlp import FusedMLP, GroupedMLP
+from ..ops.pull_box_sparse import SlotBatch, sparse_embedding_pool
+from ..ops.seqpool import SeqpoolAttrs
+
+
+class CTRModelBase(nn.Module):
+    n_labels = 1
+
+    def __init__(self, num_slots: int, embedx_dim: int, dense_dim: int, use_data_norm: bool = False,
+                 seqpool_attrs: SeqpoolAttrs | None = None):
+        super().__init__()
+        self.num_slots, self.embedx_dim, self.dense_dim = num_slots, embedx_dim, dense_dim
+        self.slot_width = 3 + embedx_dim
+        self.attrs = seqpool_attrs or SeqpoolAttrs(use_cvm=True, cvm_offset=2)
+        self.sparse_width = num_slots * self.attrs.out_width(self.slot_width)
+        self.input_width = self.sparse_width + dense_dim
+        self.data_norm = F.DataNorm(self.input_width) if use_data_norm else None
+
+    # ---- shared front end --------------------------------------------------------------
+    def split_dense(self, batch: SlotBatch):
+        d = batch.dense
+        labels = d[:, :self.n_labels]
+        feats = d[:, self.n_labels:self.n_labels + self.dense_dim]
+        return labels, feats
+
+    def sparse_features(self, batch: SlotBatch, click: torch.Tensor) -> torch.Tensor:
+        """[B, S*Eo] pooled slot embeddings; ``click`` [B] becomes the clk column of the push."""
+        cvm = torch.stack([torch.ones_like(click), click], 1)
+        return sparse_embedding_pool(batch, cvm, BoxWrapper.get_instance(), self.attrs)
+
+    def features(self, batch: SlotBatch):
+        labels, feats = self.split_dense(batch)
+        pooled = self.sparse_features(batch, labels[:, 0].contiguous())
+        x = torch.cat([pooled, feats], 1) if self.dense_dim else pooled
+        if self.data_norm is not None:
+            x = self.data_norm(x)
+        return x, pooled, labels
+
+    def dense_towers(self):
+        return [m for m in self.modules() if isinstance(m, FusedMLP)]
+
+    def mark_weights_dirty(self):
+        for m in self.dense_towers():
+            m.mark_weights_dirty()
+
+    def named_dense_params(self):
+        """(checkpoint name, parameter) pairs with the reference's naming."""
+        seen = set()
+        for m in self.dense_towers():
+            for n, p in m.named_dense_params():
+                seen.add(id(p))
+                yield n, p
+        for n, p in self.named_parameters():
+            if id(p) not in seen:
+                yield n.replace(".", "_"), p
+        if self.data_norm is not None:
+            for suffix in ("batch_size", "batch_sum", "batch_square_sum"):
+                yield f"{self.data_norm.name}.{suffix}", getattr(self.data_norm, suffix)
+
+
+class CtrDnn(CTRModelBase):
+    """Plain DNN over pooled slot embeddings + dense features (BASELINE config 1)."""
+
+    def __init__(self, num_slots=26, embedx_dim=8, dense_dim=13, hidden=(512, 256, 128), **kw):
+        super().__init__(num_slots, embedx_dim, dense_dim, **kw)
+        self.tower = FusedMLP([self.input_width, *hidden, 1], name="fc")
+
+    def forward(self, batch: SlotBatch):
+        x, _, labels = self.features(batch)
+        logit = self.tower(x).view(-1)
+        loss, pred = F.sigmoid_log_loss(logit, labels[:, 0])
+        return loss, {"pred": pred, "label": labels[:, 0]}
+
+
+class WideDeep(CTRModelBase):
+    """Wide (first-order weights of every slot + linear dense) & Deep (BASELINE config 2)."""
+
+    def __init__(self, num_slots=26, embedx_dim=8, dense_dim=13, hidden=(512, 256, 128), **kw):
+        super().__init__(num_slots, embedx_dim, dense_dim, **kw)
+        self.tower = FusedMLP([self.input_width, *hidden, 1], name="deep_fc")
+        self.wide_dense = nn.Parameter(torch.zeros(max(dense_dim, 1)))
+        self.wide_bias = nn.Parameter(torch.zeros(1))
+
+    def forward(self, batch: SlotBatch):
+        x, pooled, labels = self.features(batch)
+        E = self.attrs.out_width(self.slot_width)
+        wide = pooled.view(-1, self.num_slots, E)[:, :, 2].sum(1)      # sum of embed_w
+        if self.dense_dim:
+            wide = wide + x[:, self.sparse_width:] @ self.wide_dense
+        logit = self.tower(x).view(-1) + wide + self.wide_bias
+        loss, pred = F.sigmoid_log_loss(logit, labels[:, 0])
+        return loss, {"pred": pred, "label": labels[:, 0]}
+
+
+class DeepFM(CTRModelBase):
+    """FM first + second order over slot embeddings, plus a deep tower (BASELINE config 3)."""
+
+    def __init__(self, num_slots=26, embedx_dim=16, dense_dim=13, hidden=(512, 256, 128), **kw):
+        super().__init__(num_slots, embedx_dim, dense_dim, **kw)
+        self.tower = FusedMLP([self.input_width, *hidden, 1], name="fc")
+        self.bias = nn.Parameter(torch.zeros(1))
+
+    def forward(self, batch: SlotBatch):
+        x, pooled, labels = self.features(batch)
+        E = self.attrs.out_width(self.slot_width)
+        fm = F.fm_interaction(pooled, self.num_slots, E, 2, 3, self.embedx_dim)
+        logit = self.tower(x).view(-1) + fm + self.bias
+        loss, pred = F.sigmoid_log_loss(logit, labels[:, 0])
+        return loss, {"pred": pred, "label": labels[:, 0]}
+
+
+class MMoE(CTRModelBase):
+    """Multi-gate mixture of experts for multi-task CTR/CVR (BASELINE config 4): shared
+    expert towers (grouped tcgen05 GEMMs), one softmax gate and one tower per task."""
+
+    def __init__(self, num_slots=300, embedx_dim=64, dense_dim=0, num_experts=8, expert_hidden=(1024, 512),
+                 tower_hidden=(256, 128), num_tasks=2, **kw):
+        self.n_labels = num_tasks
+        super().__init__(num_slots, embedx_dim, dense_dim, **kw)
+        self.num_experts, self.num_tasks = num_experts, num_tasks
+        self.experts = GroupedMLP(num_experts, [self.input_width, *expert_hidden], final_relu=True, name="expert")
+        self.gates = nn.ModuleList([FusedMLP([self.input_width, num_experts], name=f"gate{t}")
+                                    for t in range(num_tasks)])
+        self.towers = nn.ModuleList([FusedMLP([expert_hidden[-1], *tower_hidden, 1], name=f"tower{t}")
+                                     for t in range(num_tasks)])
+
+    def forward(self, batch: SlotBatch):
+        x, _, labels = self.features(batch)
+        ex = self.experts(x)                                   # [E, B, H]
+        losses, preds = [], []
+        for t in range(self.num_tasks):
+            g = torch.softmax(self.gates[t](x), dim=1)         # [B, E]
+            mix = torch.einsum("be,ebh->bh", g, ex)
+            logit = self.towers[t](mix).view(-1)
+            l, p = F.sigmoid_log_loss(logit, labels[:, t])
+            losses.append(l)
+            preds.append(p)
+        loss = torch.stack(losses).sum()
+        out = {"pred": preds[0], "label": labels[:, 0]}
+        for t in range(self.num_tasks):
+            out[f"pred_{t}"] = preds[t]
+            out[f"label_{t}"] = labels[:, t]
+        return loss, out
+
+
+MODEL_REGISTRY = {"ctr_dnn": CtrDnn, "wide_deep": WideDeep, "deepfm": DeepFM, "mmoe": MMoE}
+
+
+def build_model(name: str, **kw) -> CTRModelBase:
+    return MODEL_REGISTRY[name](**kw)

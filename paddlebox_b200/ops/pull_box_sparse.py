@@ -1,0 +1,181 @@
+"""``pull_box_sparse`` / ``push_box_sparse`` and the fused embedding+pool op.
+
+Reference: ``fluid.layers._pull_box_sparse`` (python/paddle/fluid/layers/nn.py:793) and the
+operator pair (operators/pull_box_sparse_op.h:92-211): N id tensors -> N embedding tensors
+``[n_i, size]`` with columns ``[show, clk, embed_w, embedx...]``; the grad op *is* the sparse
+optimizer step (no dense gradient flows out).  ``_pull_box_extended_sparse``
+(contrib/layers/nn.py:1678; operators/pull_box_extended_sparse_op.h:25-193) adds a second
+"expand" embedding.
+
+Two entry points:
+
+* ``pull_box_sparse(batch)``                — API parity: materialises the [N, size] embeddings
+  (all slots in one tensor, ``split_by_slot`` gives the reference's per-slot list); backward
+  merges per-occurrence gradients and pushes.
+* ``sparse_embedding_pool(batch, cvm, ...)`` — the fast path every model here uses: pull and
+  ``fused_seqpool_cvm`` fused, pooled output read straight from the de-duplicated value
+  buffer; backward is ONE kernel doing seqpool/CVM backward + merge-by-key + all-to-all +
+  optimizer (csrc/cuda/sparse_a2a.cu ``k_sparse_push`` mode 0).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass
+
+import torch
+
+from .. import _native as N
+from ..box_wrapper import BoxWrapper
+from . import reference as R
+from .seqpool import SeqpoolAttrs, seqpool_cvm_forward, seqpool_cvm_backward
+
+
+@dataclass
+class SlotBatch:
+    """One mini-batch of sparse ids in the slot-major layout all sparse ops consume."""
+    keys: torch.Tensor            # int64 [N], ordered by (slot, instance)
+    lod: torch.Tensor             # int32 [S*B + 1] bag offsets, bag = slot * B + ins
+    batch_size: int
+    num_slots: int
+    dense: torch.Tensor | None = None     # fp32 [B, dense_dim] (label + dense features)
+    n_keys: int | None = None             # host-known N (avoids a sync); None -> keys.numel()
+    ins_ids: list | None = None
+    meta: dict | None = None              # search_id / rank / cmatch tensors
+
+    @property
+    def N(self) -> int:
+        return self.keys.numel() if self.n_keys is None else self.n_keys
+
+    def key2slot(self) -> torch.Tensor:
+        n = self.N
+        out = torch.empty(max(n, 1), dtype=torch.int32, device=self.keys.device)
+        if self.keys.is_cuda:
+            N.check(N.cuda().pbx_key2slot(N.ptr(self.lod), self.batch_size, self.num_slots, C.c_int64(n),
+                                          N.ptr(out), N.stream_ptr()))
+        else:
+            ends = self.lod[self.batch_size::self.batch_size].long()
+            out[:n] = torch.bucketize(torch.arange(n), ends, right=True).int()
+        return out[:n]
+
+    def slot_ranges(self):
+        """[(begin, end)] of every slot's rows in the slot-major key order (host sync)."""
+        b = self.lod[::self.batch_size].tolist()
+        return list(zip(b[:-1], b[1:]))
+
+
+_ANCHORS: dict = {}
+
+
+def _anchor(device) -> torch.Tensor:
+    """A requires-grad scalar that ties sparse ops into the autograd graph so that their
+    backward (the push) runs even though ids carry no gradient."""
+    a = _ANCHORS.get(device)
+    if a is None:
+        a = _ANCHORS[device] = torch.zeros(1, device=device, requires_grad=True)
+    return a
+
+
+class _PullBoxSparse(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, anchor, box, batch, size, offset):
+        keys = batch.keys
+        vals, restore = box.pull_sparse(keys)
+        n = batch.N
+        hidden = box.hidden
+        width = size - 0
+        if keys.is_cuda:
+            out = torch.empty(max(n, 1), hidden - offset, dtype=torch.float32, device=keys.device)
+            N.check(N.cuda().pbx_pull_scatter(N.ptr(vals), vals.stride(0), N.ptr(restore), C.c_int64(n), hidden,
+                                              offset, C.c_float(box.pull_embedx_scale), N.ptr(out), N.stream_ptr()))
+            out = out[:n]
+        else:
+            out = vals[restore.long()][:, offset:hidden].clone()
+            if box.pull_embedx_scale != 1.0:
+                out[:, max(3 - offset, 0):] *= box.pull_embedx_scale
+        ctx.box, ctx.batch, ctx.restore, ctx.offset = box, batch, restore, offset
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        box, batch, offset = ctx.box, ctx.batch, ctx.offset
+        if offset:
+            dout = torch.nn.functional.pad(dout, (offset, 0))
+        box.push_sparse_grad(batch.keys, ctx.restore, dout.contiguous(), batch.key2slot(), batch.batch_size)
+        return torch.zeros_like(_anchor(dout.device)), None, None, None, None
+
+
+def pull_box_sparse(batch: SlotBatch, size: int | None = None, offset: int = 0,
+                    box: BoxWrapper | None = None) -> torch.Tensor:
+    """Embeddings of every id of the batch, [N, size - offset] in slot-major order.
+
+    ``size`` must equal ``cvm_offset + embedx_dim`` of the BoxWrapper (default hidden 11);
+    ``offset`` skips leading cvm columns (the op's ``offset`` attr, box_wrapper.cu:92)."""
+    box = box or BoxWrapper.get_instance()
+    size = size or box.hidden
+    if size != box.hidden:
+        raise ValueError(f"pull_box_sparse size {size} != cvm_offset + embedx_dim = {box.hidden}")
+    return _PullBoxSparse.apply(_anchor(batch.keys.device), box, batch, size, offset)
+
+
+def split_by_slot(emb: torch.Tensor, batch: SlotBatch, pad_empty: bool = True):
+    """The reference's output list: one [n_s, size] tensor per slot.  An empty slot yields one
+    zero row when ``FLAGS_enable_pull_box_padding_zero`` (pull_box_sparse_op.h:131-147)."""
+    from ..flags import FLAGS
+    outs = []
+    for b, e in batch.slot_ranges():
+        if e == b and pad_empty and FLAGS.enable_pull_box_padding_zero:
+            outs.append(torch.zeros(1, emb.shape[1], dtype=emb.dtype, device=emb.device))
+        else:
+            outs.append(emb[b:e])
+    return outs
+
+
+def pull_box_extended_sparse(batch: SlotBatch, size: int, extend_size: int, box: BoxWrapper | None = None):
+    """(emb [N, size], emb_extend [N, extend_size]): the table row's embedx holds
+    ``embedx_dim = (size - 3) + extend_size`` values; the first part feeds ``emb`` and the tail
+    the expand embedding (reference PullCopyNNCross, box_wrapper.cu:146-268)."""
+    box = box or BoxWrapper.get_instance()
+    if size - 3 + extend_size != box.embedx_dim:
+        raise ValueError("size - 3 + extend_size must equal the table's embedx_dim")
+    full = _PullBoxSparse.apply(_anchor(batch.keys.device), box, batch, box.hidden, 0)
+    return full[:, :size], full[:, size:]
+
+
+class _SparseEmbeddingPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, anchor, box, batch, cvm, attrs):
+        B, S = batch.batch_size, batch.num_slots
+        vals, restore = box.pull_sparse(batch.keys)
+        out = seqpool_cvm_forward(vals, batch.lod, B, S, attrs, box.hidden, restore=restore)
+        ctx.box, ctx.batch, ctx.attrs, ctx.restore = box, batch, attrs, restore
+        ctx.save_for_backward(cvm)
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        box, batch, attrs = ctx.box, ctx.batch, ctx.attrs
+        (cvm,) = ctx.saved_tensors
+        B, S = batch.batch_size, batch.num_slots
+        if box._test_mode:
+            return torch.zeros_like(_anchor(dout.device)), None, None, None, None
+        fused_ok = (dout.is_cuda and attrs.cvm_offset == 2 and attrs.embedx_concate_size == 1
+                    and attrs.variant == 0)
+        if fused_ok:
+            Eo = attrs.out_width(box.hidden)
+            box.engine.push_pooled(ctx.restore, dout.contiguous(), cvm.contiguous(), batch.lod, B, S, Eo, 2,
+                                   attrs.dim_off(), -float(B))
+        else:
+            dx = seqpool_cvm_backward(dout.contiguous(), cvm, batch.lod, B, S, batch.N, attrs, box.hidden)
+            box.push_sparse_grad(batch.keys, ctx.restore, dx, batch.key2slot(), B)
+        return torch.zeros_like(_anchor(dout.device)), None, None, None, None
+
+
+def sparse_embedding_pool(batch: SlotBatch, cvm: torch.Tensor, box: BoxWrapper | None = None,
+                          attrs: SeqpoolAttrs | None = None, **kw) -> torch.Tensor:
+    """pull_box_sparse + fused_seqpool_cvm in one differentiable op -> [B, S*Eo].
+
+    ``cvm`` [B, 2] holds (show = 1, clk = label) per instance; in backward it becomes the
+    show/click count columns of the push."""
+    box = box or BoxWrapper.get_instance()
+    attrs = attrs or SeqpoolAttrs(**kw)
+    return _SparseEmbeddingPool.apply(_anchor(batch.keys.device), box, batch, cvm, attrs)

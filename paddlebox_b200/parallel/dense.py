@@ -1,0 +1,248 @@
+"""Dense-parameter storage, optimizer and data-parallel synchronisation.
+
+All dense parameters of a model alias ONE flat fp32 buffer and all their gradients alias ONE
+flat gradient buffer (the reference does the same with ``MemoryShareTensor`` so that the
+dense sync is one collective, boxps_worker.cc:373-392, :481-520).  On GPUs the gradient
+buffer lives in symmetric memory, so the data-parallel allreduce is the one-kernel,
+scale-fused peer-memory collective of ``parallel/symm.py`` with no packing copy
+(the reference copies every grad into a fused buffer first, c_mixallgather_op.cc:209-214).
+
+Sync modes (reference ``sync_dense_mode`` / sharding stage, boxps_worker.cc:393-395, :601-770,
+:1191-1258):
+
+* ``"allreduce"``  every step: grads summed over ranks, scaled by 1/nranks (default)
+* ``"kstep"``      K-step model averaging: no per-step sync, parameters (and optionally Adam
+                   moments, FLAGS_enable_sync_dense_moment) averaged every ``sync_weight_step``
+* ``"sharding"``   ZeRO-1: reduce-scatter grads, each rank updates its slice, all-gather params
+* ``"async"``      host-resident parameters updated by a background Adam thread
+                   (``host.AsyncDenseTable``)
+* ``"none"``       single process
+
+``FLAGS.dense_use_nccl`` routes the collectives through ``torch.distributed`` (NCCL) instead —
+the labelled baseline path, also used on CPU (gloo).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Iterable
+
+import torch
+import torch.nn as nn
+
+from .. import _native as N
+from ..flags import FLAGS
+
+
+class DenseParamStore:
+    def __init__(self, module: nn.Module, rank: int = 0, nranks: int = 1, group=None, use_symm: bool | None = None,
+                 with_moments: bool = True):
+        self.module = module
+        self.rank, self.nranks, self.group = rank, nranks, group
+        params = [p for p in module.parameters() if p.requires_grad]
+        self.params = params
+        self.device = params[0].device if params else torch.device("cpu")
+        self.cuda = self.device.type == "cuda"
+        # 16-byte aligned segments so that every tensor can be a vectorised collective operand
+        self.offsets, off = [], 0
+        for p in params:
+            self.offsets.append(off)
+            off += (p.numel() + 3) // 4 * 4
+        self.numel = max(off, 4)
+        self.use_symm = (self.cuda and nranks > 1 and not FLAGS.dense_use_nccl) if use_symm is None else use_symm
+        self.flat = torch.zeros(self.numel, dtype=torch.float32, device=self.device)
+        self.symm = None
+        if self.use_symm:
+            from .symm import SymmetricBuffer
+            # [grads | params] : the params half is only used by sharding / k-step collectives
+            self.symm = SymmetricBuffer(2 * self.numel, rank, nranks, group=group, device=self.device)
+            self.gflat = self.symm.tensor[:self.numel]
+            self.pscratch = self.symm.tensor[self.numel:]
+        else:
+            self.gflat = torch.zeros(self.numel, dtype=torch.float32, device=self.device)
+            self.pscratch = None
+        for p, o in zip(params, self.offsets):
+            n = p.numel()
+            self.flat[o:o + n].copy_(p.data.reshape(-1))
+            p.data = self.flat[o:o + n].view_as(p)
+            p.grad = self.gflat[o:o + n].view_as(p)
+        self.m = torch.zeros_like(self.flat) if with_moments else None
+        self.v = torch.zeros_like(self.flat) if with_moments else None
+        self.step_dev = torch.zeros(1, dtype=torch.float32, device=self.device)
+
+    # ---- collectives --------------------------------------------------------------------
+    def allreduce_grads(self, scale: float | None = None, stream=None) -> None:
+        """grads <- sum over ranks * scale (default 1/nranks)."""
+        if self.nranks == 1:
+            return
+        scale = 1.0 / self.nranks if scale is None else scale
+        if self.use_symm:
+            self.symm.allreduce(0, self.numel, scale, stream=stream)
+        else:
+            import torch.distributed as dist
+            dist.all_reduce(self.gflat, group=self.group)
+            self.gflat.mul_(scale)
+
+    def average_params(self, with_moments: bool = False) -> None:
+        """K-step model averaging (SyncParam, boxps_worker.cc:1191-1258)."""
+        if self.nranks == 1:
+            return
+        bufs = [self.flat] + ([self.m, self.v] if with_moments and self.m is not None else [])
+        for b in bufs:
+            if self.use_symm:
+                self.pscratch.copy_(b)
+                self.symm.allreduce(self.numel, self.numel, 1.0 / self.nranks)
+                b.copy_(self.pscratch)
+            else:
+                import torch.distributed as dist
+                dist.all_reduce(b, group=self.group)
+                b.mul_(1.0 / self.nranks)
+
+    def shard_range(self):
+        chunk = ((self.numel + self.nranks - 1) // self.nranks + 3) // 4 * 4
+        b = min(self.numel, self.rank * chunk)
+        return b, min(self.numel, b + chunk)
+
+    def reduce_scatter_grads(self) -> None:
+        if self.nranks == 1:
+            return
+        if self.use_symm:
+            self.symm.collective("reduce_scatter", 0, self.numel, 1.0 / self.nranks)
+        else:
+            import torch.distributed as dist
+            dist.all_reduce(self.gflat, group=self.group)
+            self.gflat.mul_(1.0 / self.nranks)
+
+    def all_gather_params(self) -> None:
+        if self.nranks == 1:
+            return
+        if self.use_symm:
+            b, e = self.shard_range()
+            self.pscratch[b:e].copy_(self.flat[b:e])
+            self.symm.collective("all_gather", self.numel, self.numel, 1.0)
+            self.flat.copy_(self.pscratch)
+        else:
+            import torch.distributed as dist
+            b, e = self.shard_range()
+            mask = torch.zeros_like(self.flat)
+            mask[b:e] = self.flat[b:e]
+            dist.all_reduce(mask, group=self.group)
+            self.flat.copy_(mask)
+
+    def broadcast_params(self, root: int = 0) -> None:
+        if self.nranks == 1:
+            return
+        import torch.distributed as dist
+        dist.broadcast(self.flat, src=root, group=self.group)
+
+    def zero_grad(self) -> None:
+        self.gflat.zero_()
+
+    def mark_dirty(self) -> None:
+        fn = getattr(self.module, "mark_weights_dirty", None)
+        if fn:
+            fn()
+
+
+class DenseOptimizer:
+    """Fused flat Adam / SGD over a ``DenseParamStore`` (one kernel for every parameter;
+    the reference runs one ``adam`` op per parameter)."""
+
+    def __init__(self, store: DenseParamStore, lr: float = 1e-3, betas=(0.9, 0.999), eps: float = 1e-8,
+                 weight_decay: float = 0.0, kind: str = "adam"):
+        self.store, self.lr, self.betas, self.eps, self.weight_decay, self.kind = store, lr, betas, eps, \
+            weight_decay, kind
+        self.t = 0
+
+    def step(self, grad_scale: float = 1.0, zero_grad: bool = True, lo: int = 0, hi: int | None = None) -> None:
+        s = self.store
+        hi = s.numel if hi is None else hi
+        n = hi - lo
+        if n <= 0:
+            return
+        self.t += 1
+        if s.cuda:
+            lib = N.cuda()
+            if self.kind == "adam":
+                N.check(lib.pbx_adam_flat(N.ptr(s.flat[lo:]), N.ptr(s.gflat[lo:]), N.ptr(s.m[lo:]), N.ptr(s.v[lo:]),
+                                          C.c_int64(n), C.c_float(self.lr), C.c_float(self.betas[0]),
+                                          C.c_float(self.betas[1]), C.c_float(self.eps),
+                                          C.c_float(self.weight_decay), C.c_float(grad_scale), N.ptr(s.step_dev),
+                                          int(zero_grad), N.stream_ptr()), "pbx_adam_flat")
+            else:
+                N.check(lib.pbx_sgd_flat(N.ptr(s.flat[lo:]), N.ptr(s.gflat[lo:]), C.c_int64(n), C.c_float(self.lr),
+                                         C.c_float(grad_scale), int(zero_grad), N.stream_ptr()), "pbx_sgd_flat")
+        else:
+            g = s.gflat[lo:hi] * grad_scale
+            p = s.flat[lo:hi]
+            if self.kind == "adam":
+                b1, b2 = self.betas
+                if self.weight_decay:
+                    g = g + self.weight_decay * p
+                s.m[lo:hi].mul_(b1).add_(g, alpha=1 - b1)
+                s.v[lo:hi].mul_(b2).addcmul_(g, g, value=1 - b2)
+                c1, c2 = 1 - b1 ** self.t, 1 - b2 ** self.t
+                p.sub_(self.lr / c1 * s.m[lo:hi] / ((s.v[lo:hi] / c2).sqrt() + self.eps))
+            else:
+                p.sub_(self.lr * g)
+            if zero_grad:
+                s.gflat[lo:hi].zero_()
+        s.mark_dirty()
+
+
+class DenseSync:
+    """One object per trainer that applies the configured sync mode around the optimizer step."""
+
+    def __init__(self, store: DenseParamStore, opt: DenseOptimizer, mode: str = "allreduce",
+                 sync_weight_step: int = 1, async_table=None):
+        if store.nranks == 1 and mode in ("allreduce", "kstep", "sharding"):
+            mode = "none"
+        self.store, self.opt, self.mode, self.k = store, opt, mode, max(1, sync_weight_step)
+        self.async_table = async_table
+        self.steps = 0
+        if mode == "async":
+            from ..host import AsyncDenseTable
+            self.async_table = async_table or AsyncDenseTable(store.numel, lr=opt.lr)
+            if store.rank == 0 or async_table is None:
+                self.async_table.set_params(store.flat)
+
+    def before_forward(self) -> None:
+        if self.mode == "async":
+            # PullDense: whole parameter vector host -> device (boxps_worker.cc:1300-1302)
+            self.async_table.pull(out=self.store.flat)
+            self.store.mark_dirty()
+
+    def after_backward(self) -> None:
+        s, o = self.store, self.opt
+        self.steps += 1
+        if self.mode == "none":
+            o.step()
+        elif self.mode == "allreduce":
+            s.allreduce_grads()
+            o.step()
+        elif self.mode == "kstep":
+            o.step()
+            if self.steps % self.k == 0:
+                s.average_params(FLAGS.enable_sync_dense_moment)
+                s.mark_dirty()
+        elif self.mode == "sharding":
+            s.reduce_scatter_grads()
+            b, e = s.shard_range()
+            o.step(lo=b, hi=e, zero_grad=False)
+            s.zero_grad()
+            s.all_gather_params()
+            s.mark_dirty()
+        elif self.mode == "async":
+            self.async_table.push(s.gflat)      # PushDense (D2H of the gradient vector)
+            s.zero_grad()
+        else:
+            raise ValueError(f"unknown dense sync mode {self.mode!r}")
+
+    def finalize(self) -> None:
+        """End of pass: make replicas identical again (boxps_worker.cc:1347-1356)."""
+        if self.mode == "kstep":
+            self.store.average_params(FLAGS.enable_sync_dense_moment)
+            self.store.mark_dirty()
+        elif self.mode == "async":
+            self.async_table.wait()
+            self.async_table.pull(out=self.store.flat)
+            self.store.mark_dirty()

@@ -1,0 +1,184 @@
+"""Training runtime: one process per GPU, one ``CTRTrainer`` per process.
+
+Reference roles: ``Executor.train_from_dataset`` (python/paddle/fluid/executor.py:1787-1933),
+``BoxPSTrainer`` (framework/boxps_trainer.cc: one worker thread per GPU) and ``BoxPSWorker``
+(framework/boxps_worker.cc:1278-1482: per-batch op loop, dense sync, NaN/Inf check, AUC hook,
+dump, per-op profiler).  The op-list interpreter, scopes and eager GC of the reference are
+replaced by PyTorch autograd + the CUDA caching allocator; what remains is the per-batch
+loop and everything wrapped around it.
+"""
+from __future__ import annotations
+
+import time
+from dataclasses import dataclass, field
+
+import torch
+
+from .box_wrapper import BoxWrapper
+from .flags import FLAGS
+from .parallel.dense import DenseOptimizer, DenseParamStore, DenseSync
+from .utils.nan_inf import check_batch_nan_inf
+from .utils.timer import CudaStageTimers
+
+
+@dataclass
+class TrainerConfig:
+    """Mirror of ``BoxPSWorkerParameter`` / ``TrainerDesc`` fields the reference exposes
+    (trainer_desc.proto:78, :121-129; device_worker.py:623-655)."""
+    dense_lr: float = 1e-3
+    dense_optimizer: str = "adam"
+    sync_dense_mode: str = "allreduce"     # allreduce | kstep | sharding | async | none
+    sync_weight_step: int = 1
+    async_mode: bool = False
+    debug: bool = False                    # TrainFilesWithProfiler: per-stage device timing
+    check_nan_inf: bool | None = None
+    dump_fields: list = field(default_factory=list)
+    dump_fields_path: str = ""
+    dump_param: list = field(default_factory=list)
+    dump_mode: int = 0
+    dump_interval: int = 10
+    dump_thread_num: int = 1
+    is_test: bool = False
+
+
+class CTRTrainer:
+    def __init__(self, model: torch.nn.Module, box: BoxWrapper | None = None, config: TrainerConfig | None = None,
+                 rank: int | None = None, world_size: int | None = None, group=None):
+        self.model = model
+        self.box = box or BoxWrapper.get_instance()
+        self.cfg = config or TrainerConfig()
+        self.rank = self.box.rank if rank is None else rank
+        self.world = self.box.world_size if world_size is None else world_size
+        mode = "async" if self.cfg.async_mode else self.cfg.sync_dense_mode
+        if FLAGS.padbox_enable_sharding_stage:
+            mode = "sharding"
+        self.store = DenseParamStore(model, self.rank, self.world, group)
+        self.opt = DenseOptimizer(self.store, lr=self.cfg.dense_lr, kind=self.cfg.dense_optimizer)
+        self.sync = DenseSync(self.store, self.opt, mode, self.cfg.sync_weight_step)
+        if self.world > 1:
+            self.store.broadcast_params(0)
+            self.store.mark_dirty()
+        self.timers = CudaStageTimers(self.cfg.debug)
+        self.dumper = None
+        if self.cfg.dump_fields_path and (self.cfg.dump_fields or self.cfg.dump_param):
+            from .utils.dump import FieldDumper
+            self.dumper = FieldDumper(self.cfg.dump_fields_path, self.cfg.dump_fields, self.cfg.dump_mode,
+                                      self.cfg.dump_interval, self.cfg.dump_thread_num, rank=self.rank)
+        self.steps = 0
+        self.last_outputs = None
+        for m in model.modules():
+            if getattr(m, "sync_stats", False) and self.world > 1:
+                m.reduce_fn = self._reduce_stats
+
+    def _reduce_stats(self, stats: torch.Tensor) -> torch.Tensor:
+        import torch.distributed as dist
+        dist.all_reduce(stats, group=self.store.group)
+        return stats / self.world
+
+    # ---- one mini-batch ------------------------------------------------------------------
+    def train_step(self, batch) -> torch.Tensor:
+        """forward + backward (= sparse push) + dense sync/update.  Returns the loss tensor
+        (device; reading it is the caller's sync point)."""
+        t = self.timers
+        self.sync.before_forward()
+        with t.span("forward"):
+            loss, outs = self.model(batch)
+        if self.cfg.is_test:
+            self._after_batch(batch, loss, outs)
+            return loss
+        with t.span("backward+push"):
+            loss.backward()
+        with t.span("dense_sync+opt"):
+            self.sync.after_backward()
+        self._after_batch(batch, loss, outs)
+        return loss
+
+    def infer_step(self, batch):
+        with torch.no_grad():
+            loss, outs = self.model(batch)
+        self.box.add_metric_data(outs)
+        return loss, outs
+
+    def _after_batch(self, batch, loss, outs):
+        self.steps += 1
+        self.last_outputs = outs
+        check = FLAGS.check_nan_inf if self.cfg.check_nan_inf is None else self.cfg.check_nan_inf
+        if check:
+            check_batch_nan_inf({"loss": loss, **{k: v for k, v in outs.items() if torch.is_tensor(v)}},
+                                self.cfg.dump_fields_path or None, tag=f"rank{self.rank}_step{self.steps}")
+        self.box.add_metric_data(outs)           # AddAucMonitor
+        if self.dumper is not None and self.cfg.dump_fields and batch.ins_ids is not None:
+            self.dumper.dump_batch(batch.ins_ids, outs)
+
+    # ---- one pass ---------------------------------------------------------------------------
+    def train_from_dataset(self, dataset, print_period: int = 0, fetch_handler=None) -> dict:
+        """Train every batch the dataset dealt to this worker; returns pass statistics."""
+        if dataset._prepared_workers == 0:
+            dataset.prepare_train(self.world, self.rank)
+        t0 = time.time()
+        n_ins, losses = 0, []
+        want_ids = self.dumper is not None and bool(self.cfg.dump_fields)
+        for i, batch in enumerate(dataset.batches(worker=self.rank, with_ins_id=want_ids)):
+            loss = self.train_step(batch)
+            n_ins += batch.batch_size
+            if print_period and (i + 1) % print_period == 0:
+                losses.append(float(loss))
+                if fetch_handler:
+                    fetch_handler(i + 1, losses[-1])
+        self.sync.finalize()
+        if self.box.use_cuda:
+            torch.cuda.synchronize()
+            if self.box.engine is not None:
+                self.box.engine.check_status()
+        if self.dumper is not None and self.cfg.dump_param:
+            named = dict(self.model.named_dense_params()) if hasattr(self.model, "named_dense_params") \
+                else dict(self.model.named_parameters())
+            self.dumper.dump_params([(n, named[n]) for n in self.cfg.dump_param if n in named])
+        dt = time.time() - t0
+        stats = {"instances": n_ins, "seconds": dt, "ins_per_sec": n_ins / max(dt, 1e-9), "steps": self.steps,
+                 "losses": losses}
+        if self.cfg.debug:
+            stats["stage_ms"] = self.timers.summary()   # read_time / cal_time style breakdown
+        return stats
+
+    def finalize(self):
+        if self.dumper is not None:
+            self.dumper.close()
+            self.dumper = None
+
+
+class Executor:
+    """``exe.train_from_dataset(program, dataset)`` facade: ``program`` is a model (or a
+    prepared ``CTRTrainer``)."""
+
+    def __init__(self, place=None):
+        self.place = place
+        self._trainers: dict = {}
+
+    def _trainer_for(self, program, **kw) -> CTRTrainer:
+        if isinstance(program, CTRTrainer):
+            return program
+        t = self._trainers.get(id(program))
+        if t is None:
+            cfg = kw.pop("config", None) or getattr(program, "_pipeline_opt", None)
+            t = self._trainers[id(program)] = CTRTrainer(program, config=cfg)
+        return t
+
+    def train_from_dataset(self, program, dataset, scope=None, thread=0, debug=False, fetch_list=None,
+                           fetch_info=None, print_period=100, fetch_handler=None, **kw):
+        tr = self._trainer_for(program, **kw)
+        tr.cfg.debug = tr.cfg.debug or debug
+        tr.timers.enabled = tr.cfg.debug and torch.cuda.is_available()
+        tr.cfg.is_test = False
+        return tr.train_from_dataset(dataset, print_period if fetch_handler else 0, fetch_handler)
+
+    def infer_from_dataset(self, program, dataset, **kw):
+        tr = self._trainer_for(program, **kw)
+        tr.cfg.is_test = True
+        self_box = tr.box
+        self_box.set_test_mode(True)
+        try:
+            return tr.train_from_dataset(dataset)
+        finally:
+            self_box.set_test_mode(False)
+            tr.cfg.is_test = False

@@ -1,0 +1,89 @@
+"""Field / parameter dump (reference dump_fields / dump_param written by a thread pool into
+rolling part files, boxps_worker.cc:1595-1855: one line per instance
+``lineid\\tfield:len:v1:v2...``; sampling by ``dump_mode`` / ``dump_interval``)."""
+from __future__ import annotations
+
+import os
+import queue
+import threading
+import zlib
+
+import torch
+
+
+class FieldDumper:
+    def __init__(self, path: str, fields, dump_mode: int = 0, dump_interval: int = 10, num_threads: int = 1,
+                 part_bytes: int = 2 << 30, rank: int = 0):
+        """dump_mode 0 = all instances, 1 = hash(lineid) % interval == 0, 2 = every
+        ``dump_interval``-th instance."""
+        os.makedirs(path, exist_ok=True)
+        self.path, self.fields = path, list(fields)
+        self.mode, self.interval = dump_mode, max(1, dump_interval)
+        self.part_bytes, self.rank = part_bytes, rank
+        self._q: "queue.Queue" = queue.Queue(maxsize=64)
+        self._part, self._written, self._fp = 0, 0, None
+        self._seen = 0
+        self._threads = [threading.Thread(target=self._loop, daemon=True) for _ in range(max(1, num_threads))]
+        self._lock = threading.Lock()
+        for t in self._threads:
+            t.start()
+
+    def _open(self):
+        if self._fp:
+            self._fp.close()
+        self._fp = open(os.path.join(self.path, f"part-{self.rank:03d}-{self._part:05d}"), "w")
+        self._part += 1
+        self._written = 0
+
+    def _loop(self):
+        while True:
+            item = self._q.get()
+            if item is None:
+                self._q.task_done()
+                return
+            text = "".join(item)
+            with self._lock:
+                if self._fp is None or self._written + len(text) > self.part_bytes:
+                    self._open()
+                self._fp.write(text)
+                self._written += len(text)
+            self._q.task_done()
+
+    def _keep(self, lineid: str) -> bool:
+        if self.mode == 0:
+            return True
+        if self.mode == 1:
+            return zlib.crc32(lineid.encode()) % self.interval == 0
+        self._seen += 1
+        return self._seen % self.interval == 0
+
+    def dump_batch(self, ins_ids, tensors: dict):
+        host = {k: tensors[k].detach().float().cpu().reshape(len(ins_ids), -1) for k in self.fields if k in tensors}
+        lines = []
+        for i, lid in enumerate(ins_ids):
+            if not self._keep(lid):
+                continue
+            parts = [lid]
+            for k, t in host.items():
+                row = t[i].tolist()
+                parts.append(f"{k}:{len(row)}:" + ":".join(f"{v:.6g}" for v in row))
+            lines.append("\t".join(parts) + "\n")
+        if lines:
+            self._q.put(lines)
+
+    def dump_params(self, named_params):
+        lines = []
+        for name, p in named_params:
+            flat = p.detach().float().cpu().reshape(-1).tolist()
+            lines.append(f"{name}:{len(flat)}:" + ":".join(f"{v:.6g}" for v in flat) + "\n")
+        self._q.put(lines)
+
+    def close(self):
+        self._q.join()
+        for _ in self._threads:
+            self._q.put(None)
+        for t in self._threads:
+            t.join()
+        if self._fp:
+            self._fp.close()
+            self._fp = None

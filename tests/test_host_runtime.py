@@ -1,0 +1,281 @@
+"""Host C++ runtime: parser, batch dealing, dataset, host table, AUC, checkpoints (CPU)."""
+import math
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from paddlebox_b200 import _native as N
+from paddlebox_b200.host import HostAuc, HostTable, NativeDataset, compute_batch_ranges, AsyncDenseTable
+from paddlebox_b200.ops import reference as R
+from tests.util_data import slot_vars, write_files
+
+
+# ---------------------------------------------------------------- parser
+def _ds(vars_):
+    d = NativeDataset()
+    d.set_slots([v.desc() for v in vars_])
+    return d
+
+
+def test_parse_line_basic_and_drops_zero_feasigns():
+    from paddlebox_b200.dataset import dense_slot, sparse_slot
+    d = _ds([dense_slot("label", 1), sparse_slot("a"), sparse_slot("b")])
+    u, f, _ = d.parse_line("1 1.0 3 11 0 13 1 7")
+    assert u.tolist() == [11, 13, 7]          # zero feasign dropped (data_feed.cc:4099)
+    assert f.tolist() == [1.0]
+    assert d.parse_line("1 1.0 1 0 1 0") is None          # no feasign at all -> rejected
+    assert d.parse_line("1 1.0 0 1 7") is None             # n == 0 is illegal
+    assert d.parse_line("1 1.0 2 5") is None                # truncated
+
+
+def test_parse_line_ins_id_logkey_and_unused_slot():
+    from paddlebox_b200.data_generator import make_logkey
+    from paddlebox_b200.dataset import dense_slot, sparse_slot, SlotVar
+    d = NativeDataset()
+    slots = [dense_slot("label", 1), SlotVar("skipme", "int64", 1, (-1, 1), is_used=False), sparse_slot("a")]
+    d.set_slots([s.desc() for s in slots])
+    d.set("parse_ins_id", 1)
+    d.set("parse_logkey", 1)
+    lk = make_logkey(0xabcdef12345, 0x0de, 2)
+    u, f, sid = d.parse_line(f"1 ins_42 1 {lk} 1 0.0 2 99 98 1 5")
+    assert u.tolist() == [5] and sid == 0xabcdef12345
+
+
+# ---------------------------------------------------------------- batch dealing
+@pytest.mark.parametrize("n,bs,w", [(1000, 64, 4), (8 * 64 * 3 + 5, 64, 8), (100, 64, 8), (7, 4, 8), (4096 * 9, 4096, 8),
+                                    (129, 16, 2)])
+def test_batch_ranges_equal_counts(n, bs, w):
+    r = compute_batch_ranges(n, bs, w)
+    assert sum(l for _, l in r) == n
+    assert len(r) % w == 0                         # every worker gets the same number of batches
+    pos = 0
+    for s, l in r:
+        assert s == pos and l >= 0
+        pos += l
+    assert max(l for _, l in r) <= max(bs, n // w + n % w) * 2
+
+
+# ---------------------------------------------------------------- dataset
+def test_dataset_load_shuffle_batches(tmp_path):
+    vars_ = slot_vars(6, 3)
+    files = write_files(str(tmp_path), n_files=3, lines_per_file=101, n_sparse=6, n_dense=3, key_space=50)
+    d = _ds(vars_)
+    d.set_filelist(files)
+    d.set("thread_num", 2)
+    d.set("batch_size", 32)
+    d.load_into_memory()
+    assert d.num_records() == 303
+    uk = d.unique_keys()
+    assert uk[0] == 0 and len(np.unique(uk)) == len(uk)   # key 0 always registered
+    d.prepare_train(2, True, 7, 0)
+    assert d.num_batches(0) == d.num_batches(1) > 0
+    seen_keys = set()
+    total = 0
+    for w in range(2):
+        for b in range(d.num_batches(w)):
+            B, n = d.batch_shape(w, b)
+            keys = np.zeros(n, dtype=np.uint64)
+            off = np.zeros(6 * B + 1, dtype=np.int32)
+            dense = np.zeros((B, 4), dtype=np.float32)
+            d.pack_batch(w, b, keys.ctypes.data, off.ctypes.data, dense.ctypes.data, True)
+            assert off[-1] == n and np.all(np.diff(off) >= 1)
+            assert set(np.unique(dense[:, 0])) <= {0.0, 1.0}
+            seen_keys |= set(keys.tolist())
+            total += B
+            # record-major packing holds the same multiset of keys
+            keys2 = np.zeros(n, dtype=np.uint64)
+            off2 = np.zeros(B * 7, dtype=np.int32)
+            d.pack_batch(w, b, keys2.ctypes.data, off2.ctypes.data, dense.ctypes.data, False)
+            assert sorted(keys2.tolist()) == sorted(keys.tolist())
+    assert total == 303
+    assert seen_keys | {0} == set(uk.tolist())
+
+
+def test_dataset_pipe_command_sample_rate_archive(tmp_path):
+    vars_ = slot_vars(3, 0)
+    files = write_files(str(tmp_path), n_files=1, lines_per_file=400, n_sparse=3, n_dense=0, key_space=30)
+    d = _ds(vars_)
+    d.set_filelist(files)
+    d.set("pipe_command", "head -n 100")
+    d.load_into_memory()
+    assert d.num_records() == 100
+    arch = str(tmp_path / "arch.bin")
+    d.save_archive(arch)
+    keys_before = d.unique_keys()
+    d2 = _ds(vars_)
+    d2.load_archive(arch)
+    assert d2.num_records() == 100 and np.array_equal(d2.unique_keys(), keys_before)
+    d3 = _ds(vars_)
+    d3.set_filelist(files)
+    d3.set("sample_rate", 0.5)
+    d3.load_into_memory()
+    assert 120 < d3.num_records() < 280
+
+
+def test_dataset_preload_and_slots_shuffle(tmp_path):
+    vars_ = slot_vars(4, 0)
+    files = write_files(str(tmp_path), n_files=2, lines_per_file=50, n_sparse=4, n_dense=0, key_space=1000)
+    d = _ds(vars_)
+    d.set_filelist(files)
+    d.preload_into_memory()
+    d.wait_preload_done()
+    assert d.num_records() == 100
+    d.prepare_train(1, False, 0, 0)
+
+    def slot_keys(slot):
+        out = []
+        for b in range(d.num_batches(0)):
+            B, n = d.batch_shape(0, b)
+            keys = np.zeros(n, dtype=np.uint64)
+            off = np.zeros(4 * B + 1, dtype=np.int32)
+            d.pack_batch(0, b, keys.ctypes.data, off.ctypes.data, 0, True)
+            out.append(keys[off[slot * B]:off[(slot + 1) * B]].tolist())
+        return out
+    before0, before1 = slot_keys(1), slot_keys(0)
+    d.slots_shuffle([2], 3)     # index 2 in the slot list = sparse slot1 (label is slot 0)
+    after0, after1 = slot_keys(1), slot_keys(0)
+    assert after1 == before1                              # untouched slot
+    assert sorted(sum(after0, [])) == sorted(sum(before0, [])) and after0 != before0
+
+
+def test_parser_plugin(tmp_path):
+    """A user parser .so (role of ISlotParser plugins, data_feed.cc:3604-3670)."""
+    import subprocess
+    src = tmp_path / "plug.cc"
+    src.write_text(r'''
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+extern "C" int pbx_parse_line(const char* line, size_t len, void* ctx,
+    void (*emit_u64)(void*, int, const uint64_t*, size_t), void (*emit_f32)(void*, int, const float*, size_t),
+    void (*emit_meta)(void*, const char*, uint64_t, uint32_t, uint32_t)) {
+  // format: "<label>;<k1>,<k2>,..."
+  char* end = nullptr;
+  float label = strtof(line, &end);
+  if (*end != ';') return 1;
+  std::vector<uint64_t> ks;
+  const char* p = end + 1;
+  while (p < line + len) { ks.push_back(strtoull(p, &end, 10)); if (end == p) break; p = end + 1; }
+  emit_f32(ctx, 0, &label, 1);
+  emit_u64(ctx, 1, ks.data(), ks.size());
+  emit_meta(ctx, "x", 7, 0, 0);
+  return 0;
+}''')
+    so = tmp_path / "plug.so"
+    subprocess.check_call(["g++", "-shared", "-fPIC", "-O1", "-o", str(so), str(src)])
+    data = tmp_path / "d.txt"
+    data.write_text("1;5,6,7\n0;8\n")
+    from paddlebox_b200.dataset import dense_slot, sparse_slot
+    d = NativeDataset()
+    d.set("parser_plugin", str(so))
+    d.set_slots([dense_slot("label").desc(), sparse_slot("a").desc()])
+    d.set_filelist([str(data)])
+    d.load_into_memory()
+    assert d.num_records() == 2 and set(d.unique_keys().tolist()) == {0, 5, 6, 7, 8}
+
+
+# ---------------------------------------------------------------- host table
+@pytest.mark.parametrize("opt", ["adagrad", "adam", "shared_adam"])
+def test_host_table_matches_python_oracle(opt):
+    cfg = N.SparseOptConfig(mf_create_thresholds=2.0, mf_initial_range=0.0)
+    t = HostTable(4, opt, cfg)
+    keys = np.arange(1, 40, dtype=np.uint64) * 13
+    t.fetch_rows(keys, create=True)
+    rows = {int(k): R.new_row(t.layout, cfg) for k in keys}
+    g = torch.Generator().manual_seed(0)
+    for _ in range(5):
+        push = torch.zeros(len(keys), t.layout.push_stride)
+        push[:, 0] = 2
+        push[:, 1] = torch.randint(1, 4, (len(keys),), generator=g).float()
+        push[:, 2] = torch.randint(0, 2, (len(keys),), generator=g).float()
+        push[:, 3:8] = torch.randn(len(keys), 5, generator=g)
+        t.push(keys, push)
+        for i, k in enumerate(keys):
+            rows[int(k)] = R.sparse_row_update(rows[int(k)], push[i].tolist(), t.layout, cfg)
+    got = t.fetch_rows(keys, create=False)
+    exp = np.array([rows[int(k)] for k in keys], dtype=np.float32)
+    assert np.allclose(got, exp, rtol=2e-4, atol=2e-5)
+    pulled = t.pull(np.concatenate([keys[:3], np.array([0, 999999], dtype=np.uint64)]))
+    assert torch.allclose(pulled[:3], torch.from_numpy(exp[:3, :7]), atol=1e-6) and torch.all(pulled[3:] == 0)
+
+
+def test_host_table_checkpoint_roundtrip_and_shrink(tmp_path):
+    cfg = N.SparseOptConfig(mf_create_thresholds=1.0)
+    t = HostTable(4, "adagrad", cfg)
+    keys = np.arange(1, 101, dtype=np.uint64)
+    t.fetch_rows(keys)
+    push = np.zeros((100, t.layout.push_stride), dtype=np.float32)
+    push[:, 1] = 30
+    push[:, 2] = 5
+    push[:, 3:8] = np.random.RandomState(0).randn(100, 5)
+    t.push(keys[:60], push[:60])
+    t.push(keys[:60], push[:60])
+    n = t.save(str(tmp_path / "batch"), mode=0)
+    assert n == 100
+    files = sorted(os.listdir(tmp_path / "batch"))
+    assert files[0].startswith("part-000-") and len(files) == 64
+    t2 = HostTable(4, "adagrad", cfg)
+    assert t2.load(str(tmp_path / "batch")) == 100
+    assert np.allclose(t2.fetch_rows(keys, create=False), t.fetch_rows(keys, create=False), rtol=1e-6, atol=1e-7)
+    # delta: only touched keys, serving format (weights only)
+    nd = t.save(str(tmp_path / "delta"), mode=1)
+    assert nd == 60
+    assert t.save(str(tmp_path / "delta2"), mode=1) == 0      # dirty flags were cleared
+    t3 = HostTable(4, "adagrad", cfg)
+    assert t3.load(str(tmp_path / "delta"), serving=True) == 60
+    a, b = t3.pull(keys[:60]), t.pull(keys[:60])
+    assert torch.allclose(a, b, rtol=1e-5, atol=1e-6)
+    kept = t.shrink(decay=0.5, delete_threshold=1.0, delete_after_unseen_days=30)
+    assert kept == 60 and t.size() == 60
+
+
+# ---------------------------------------------------------------- metrics
+def test_auc_matches_exact_and_components():
+    rs = np.random.RandomState(0)
+    pred = rs.rand(5000).astype(np.float32)
+    label = (rs.rand(5000) < pred).astype(np.float32)
+    a = HostAuc(100000)
+    a.add(pred[:2500], label[:2500])
+    a.add(pred[2500:], label[2500:])
+    auc, bucket_err, mae, rmse, actr, pctr, copc, size = a.compute()
+    # exact AUC by rank statistic
+    order = np.argsort(pred)
+    ranks = np.empty(5000)
+    ranks[order] = np.arange(1, 5001)
+    npos = label.sum()
+    exact = (ranks[label == 1].sum() - npos * (npos + 1) / 2) / (npos * (5000 - npos))
+    assert abs(auc - exact) < 2e-4
+    assert size == 5000 and abs(actr - label.mean()) < 1e-9 and abs(pctr - pred.mean()) < 1e-6
+    assert abs(mae - np.abs(pred - label).mean()) < 1e-6
+    assert abs(rmse - math.sqrt(((pred - label) ** 2).mean())) < 1e-6
+    assert abs(copc - actr / pctr) < 1e-9 and bucket_err >= 0
+    b = HostAuc(1000)
+    b.add(np.full(10, 0.3, np.float32), np.zeros(10, np.float32))
+    assert b.compute()[0] == -0.5                 # all one class (metrics.cc:323-325)
+    m = HostAuc(1000)
+    m.add(pred, label, mask=(np.arange(5000) % 2).astype(np.float32))
+    assert m.compute()[7] == 2500
+
+
+def test_wuauc():
+    a = HostAuc(1000)
+    pred = np.array([0.9, 0.1, 0.8, 0.2, 0.5, 0.6], np.float32)
+    label = np.array([1, 0, 0, 1, 1, 1], np.float32)
+    uid = np.array([1, 1, 2, 2, 3, 3], np.uint64)
+    a.add_uid(pred, label, uid)
+    uauc, wuauc, users, size = a.compute_wuauc()
+    assert users == 2 and size == 4            # user 3 has one class only
+    assert abs(uauc - 0.5) < 1e-6 and abs(wuauc - 0.5) < 1e-6
+
+
+def test_async_dense_table():
+    t = AsyncDenseTable(1000, lr=0.1, threads=2, merge_limit=4)
+    t.set_params(torch.ones(1000))
+    for _ in range(8):
+        t.push(torch.full((1000,), 0.5))
+    t.wait()
+    p = t.pull()
+    assert t.updates() >= 2 and torch.all(p < 1.0) and torch.allclose(p, p[0].expand(1000))
