@@ -1,0 +1,302 @@
+#!/usr/bin/env python
+"""Headline benchmark: DeepFM sparse-CTR training throughput (instances/sec).
+
+Config (BASELINE.json config 3): DeepFM, 1 B-key sparse table sharded over 8 GPUs
+(= 125 M keys per GPU, weak scaling: per-GPU table and per-GPU batch are fixed), embedding
+dim 16, 26 sparse slots with variable-length bags + 13 dense features, fused_seqpool_cvm,
+batch 4096 per GPU, bf16 towers / fp32 table.  Synthetic slot data and random-init weights
+(no network for datasets).
+
+One step = pull (dedup + all-to-all + lookup) -> fused seqpool/CVM -> FM + tcgen05 MLP ->
+log-loss -> backward -> push (merge + all-to-all + sparse Adagrad) -> dense grad allreduce
+-> dense Adam.  Nothing is skipped inside the timed region.
+
+    python bench.py --gpus 1 --steps 50 --warmup 5
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
+        --master-port 29500 bench.py --gpus 8 --steps 50 --warmup 5
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+
+
+def parse_args():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=30)
+    p.add_argument("--warmup", type=int, default=5)
+    p.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    p.add_argument("--batch", type=int, default=4096, help="instances per GPU per step")
+    p.add_argument("--slots", type=int, default=26)
+    p.add_argument("--dense", type=int, default=13)
+    p.add_argument("--dim", type=int, default=16)
+    p.add_argument("--max-bag", type=int, default=5, help="bag length ~ U[1, max-bag]")
+    p.add_argument("--keys-per-gpu", type=int, default=125_000_000)
+    p.add_argument("--hidden", default="512,256,128")
+    p.add_argument("--n-batches", type=int, default=8, help="distinct synthetic batches rotated through")
+    p.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
+    p.add_argument("--profile-stages", action="store_true")
+    return p.parse_args()
+
+
+def reference_arm(args):
+    # The reference is a PaddlePaddle fork whose sparse engine (libbox_ps.so) is a closed binary
+    # fetched from an internal host; /root/reference has neither setup.py nor pyproject.toml
+    # (pip: "Directory '/root/reference' is not installable") and its CMake build needs ~40
+    # network-fetched third-party projects.  See DESIGN.md "Reference arm".
+    print(json.dumps({"impl": "reference",
+                      "unavailable": "reference is not pip-installable offline (no setup.py/pyproject.toml; "
+                                     "BoxPS core libbox_ps.so is a closed binary; CMake build needs network)"}))
+    return 0
+
+
+class ClockSampler:
+    """Samples SM clocks / throttle reasons with nvidia-smi while the timed region runs."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx = gpu_index
+        self.proc = None
+        self.lines = []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.idx)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def make_host_batches(args, rank, world, n_batches, seed=1234):
+    """Synthetic batches in the dataset's record-major pinned layout:
+    keys [N] (instance-major), rec_off [B, S+1], dense [B, 1 + dense]."""
+    from paddlebox_b200.ops.sparse_table import synthetic_key
+    g = torch.Generator().manual_seed(seed + rank)
+    B, S = args.batch, args.slots
+    n_total = args.keys_per_gpu * world
+    out = []
+    for _ in range(n_batches):
+        lens = torch.randint(1, args.max_bag + 1, (B, S), generator=g)
+        n = int(lens.sum())
+        # skewed popularity: idx = floor(u^2 * n_total) (hot head, long tail), slot-disjoint ranges
+        u = torch.rand(n, generator=g, dtype=torch.float64)
+        idx = (u * u * n_total).long().clamp_(max=n_total - 1)
+        keys = synthetic_key(idx, key_seed=1)
+        off = torch.zeros(B, S + 1, dtype=torch.int32)
+        off[:, 1:] = torch.cumsum(lens, 1).int()
+        base = torch.zeros(B, dtype=torch.int32)
+        base[1:] = torch.cumsum(off[:-1, S], 0).int()
+        off += base[:, None]
+        dense = torch.rand(B, 1 + args.dense, generator=g)
+        dense[:, 0] = (dense[:, 0] < 0.2).float()
+        out.append((keys.pin_memory(), off.pin_memory(), dense.pin_memory(), n))
+    return out
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+    rank = int(os.environ.get("RANK", 0))
+    local_rank = int(os.environ.get("LOCAL_RANK", 0))
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    if world != args.gpus and world == 1 and args.gpus > 1:
+        print(f"bench.py --gpus {args.gpus} must be launched with torchrun (--nproc-per-node {args.gpus})",
+              file=sys.stderr)
+        return 2
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    import torch.distributed as dist
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    import ctypes as C
+    from paddlebox_b200 import _native as N
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    from paddlebox_b200.models.ctr import DeepFM
+    from paddlebox_b200.ops.pull_box_sparse import SlotBatch
+    from paddlebox_b200.trainer import CTRTrainer, TrainerConfig
+    lib = N.cuda()
+    lib.pbx_launch_count.restype = C.c_longlong
+
+    B, S = args.batch, args.slots
+    max_keys = B * S * args.max_bag
+    hidden = tuple(int(x) for x in args.hidden.split(","))
+    box = BoxWrapper.set_instance(embedx_dim=args.dim, rank=rank, world_size=world)
+    capacity = int(args.keys_per_gpu / 0.6) + 1024        # load factor 0.6 (< reference's 0.75)
+    box.initialize_gpu_and_load_model({"mf_create_thresholds": 10.0}, table_capacity=capacity,
+                                      max_keys_per_batch=max_keys)
+    t0 = time.time()
+    box.table.fill_synthetic(args.keys_per_gpu * world, key_seed=1, rank=rank, nranks=world, create_mf=True)
+    box._in_pass = True
+    fill_s = time.time() - t0
+    torch.manual_seed(0)
+    model = DeepFM(num_slots=S, embedx_dim=args.dim, dense_dim=args.dense, hidden=hidden).to(dev)
+    trainer = CTRTrainer(model, box, TrainerConfig(dense_lr=1e-3, sync_dense_mode="allreduce",
+                                                   debug=args.profile_stages))
+    host_batches = make_host_batches(args, rank, world, args.n_batches)
+    scratch = torch.empty(1024, dtype=torch.int32, device=dev)
+    flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=dev)    # 256 MB > 126 MB L2
+
+    def stage(hb):
+        """host (pinned) -> device + batch_build: what the dataset loader does per batch."""
+        keys_h, off_h, dense_h, n = hb
+        dk = keys_h.to(dev, non_blocking=True)
+        do = off_h.to(dev, non_blocking=True)
+        dd = dense_h.to(dev, non_blocking=True)
+        keys = torch.empty(n, dtype=torch.int64, device=dev)
+        lod = torch.empty(S * B + 1, dtype=torch.int32, device=dev)
+        N.check(lib.pbx_batch_build(N.ptr(dk), N.ptr(do), B, S, N.ptr(keys), N.ptr(lod), N.ptr(scratch),
+                                    N.stream_ptr()))
+        b = SlotBatch(keys, lod, B, S, dd, n_keys=n)
+        b._keep = (dk, do)
+        return b
+
+    h2d_bytes = sum(t.numel() * t.element_size() for t in host_batches[0][:3])
+    dev_batches = [stage(hb) for hb in host_batches]
+    torch.cuda.synchronize()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def flush():
+        if not args.no_flush:
+            N.check(lib.pbx_l2_flush(N.ptr(flush_buf), C.c_int64(flush_buf.numel()), N.stream_ptr()))
+
+    # ------------------------------------------------ device-timed steps (inputs resident)
+    for i in range(args.warmup):
+        trainer.train_step(dev_batches[i % len(dev_batches)])
+    barrier()
+    box.engine.check_status()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    launches0 = lib.pbx_launch_count()
+    evs = []
+    barrier()
+    wall0 = time.time()
+    for i in range(args.steps):
+        flush()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        loss = trainer.train_step(dev_batches[(args.warmup + i) % len(dev_batches)])
+        b.record()
+        evs.append((a, b))
+    barrier()
+    wall = time.time() - wall0
+    launches = lib.pbx_launch_count() - launches0 - (0 if args.no_flush else args.steps)
+    dev_ms = sum(a.elapsed_time(b) for a, b in evs)
+    box.engine.check_status()
+    loss_val = float(loss)
+
+    # ------------------------------------------------ end-to-end through the public API:
+    # every step copies its inputs from pinned host memory, builds the batch on the device,
+    # trains, and reads the loss back.
+    for i in range(2):
+        float(trainer.train_step(stage(host_batches[i % len(host_batches)])))
+    barrier()
+    e_evs = []
+    for i in range(args.steps):
+        flush()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        l = trainer.train_step(stage(host_batches[(i + 3) % len(host_batches)]))
+        l_host = float(l)                      # D2H read of the step's result
+        b.record()
+        e_evs.append((a, b))
+    barrier()
+    clocks = sampler.stop()
+    e2e_ms = sum(a.elapsed_time(b) for a, b in e_evs)
+    box.engine.check_status()
+
+    # max over ranks
+    t = torch.tensor([dev_ms, e2e_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    dev_ms, e2e_ms = t.tolist()
+    stage_ms = trainer.timers.summary() if args.profile_stages else None
+    if rank == 0:
+        gb = B * world
+        value = gb * args.steps / (dev_ms / 1e3)
+        e2e = gb * args.steps / (e2e_ms / 1e3)
+        out = {
+            "metric": "instances/sec (DeepFM sparse-CTR training, device-timed, max over ranks)",
+            "value": round(value, 1), "unit": "instances/s", "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": round(dev_ms / args.steps, 4), "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "impl": "ours",
+            "config": {"model": "DeepFM", "global_batch": gb, "seq_len": None,
+                       "parallelism": f"dp{world}+sparse-shard{world}", "batch_per_gpu": B, "sparse_slots": S,
+                       "dense_features": args.dense, "emb_dim": args.dim, "bag_len": f"U[1,{args.max_bag}]",
+                       "avg_keys_per_batch_per_gpu": int(sum(h[3] for h in host_batches) / len(host_batches)),
+                       "table_keys_per_gpu": args.keys_per_gpu, "table_keys_total": args.keys_per_gpu * world,
+                       "mlp": [model.input_width, *hidden, 1], "sparse_optimizer": "adagrad",
+                       "dense_optimizer": "adam", "table_dtype": "fp32", "tower_dtype": "bf16 (fp32 accumulate)",
+                       "l2": "flushed between timed steps (256 MB write)" if not args.no_flush else
+                             "not flushed; table (>= 14 GB/GPU) and rotating batches exceed L2",
+                       "table_fill_s": round(fill_s, 2)},
+            "e2e": {"value": round(e2e, 1), "unit": "instances/s", "ms_per_step": round(e2e_ms / args.steps, 4),
+                    "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": 4},
+            "gpu_launches": int(launches),
+            "clocks": clocks,
+            "loss": loss_val,
+            "wall_s_timed_region": round(wall, 3),
+        }
+        if stage_ms:
+            out["stage_ms"] = stage_ms
+        print(json.dumps(out))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

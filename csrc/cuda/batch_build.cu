@@ -109,6 +109,7 @@ int pbx_batch_build(const uint64_t* d_rec_keys, const int32_t* d_rec_off, int B,
   void* args[] = {(void*)&d_rec_keys, (void*)&d_rec_off, (void*)&B, (void*)&S, (void*)&d_keys_out,
                   (void*)&d_lod_out, (void*)&d_scratch};
   PBX_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_batch_build, dim3(blocks), dim3(BB_THREADS), args, 0, st));
+  pbx_note_launch(1);
   return 0;
 }
 

@@ -24,6 +24,10 @@ void pbx_set_error(const char* fmt, ...);
     }                                                                            \
   } while (0)
 
+// every kernel launch made by this library is counted (bench.py reports it as gpu_launches)
+extern "C" long long pbx_launch_count();
+void pbx_note_launch(int n);
+
 #define PBX_REQUIRE(cond, ...)                                                   \
   do {                                                                           \
     if (!(cond)) {                                                               \

@@ -286,7 +286,7 @@ int pbx_cast_transpose(const float* x, int ld, int M, int K, void* out_bf16, int
   dim3 grid((K + 31) / 32, (M + 31) / 32);
   k_cast_transpose<<<grid, dim3(32, 8), 0, st>>>(x, ld, M, K, (__nv_bfloat16*)out_bf16, ldo, (__nv_bfloat16*)out_t,
                                                  ldt);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
@@ -295,7 +295,7 @@ int pbx_colsum_bf16(const void* x, int ld, int M, int N, float* out, cudaStream_
   int gy = (M + 255) / 256;
   if (gy > 64) gy = 64;
   k_colsum_bf16<<<dim3((N + 31) / 32, gy), 256, 0, st>>>((const __nv_bfloat16*)x, ld, M, N, out);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
@@ -305,14 +305,14 @@ int pbx_adam_flat(float* p, float* g, float* m, float* v, int64_t n, float lr, f
   k_adam_flat<<<pbx_grid_for(n, 256, 8), 256, 0, st>>>(p, g, m, v, n, lr, b1, b2, eps, weight_decay, grad_scale,
                                                        step_dev, zero_grad);
   k_step_inc<<<1, 1, 0, st>>>(step_dev);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
 int pbx_sgd_flat(float* p, float* g, int64_t n, float lr, float grad_scale, int zero_grad, cudaStream_t st) {
   if (n <= 0) return 0;
   k_sgd_flat<<<pbx_grid_for(n, 256, 8), 256, 0, st>>>(p, g, n, lr, grad_scale, zero_grad);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
@@ -320,14 +320,14 @@ int pbx_sigmoid_logloss(const float* logit, const float* label, int B, float* pr
                         float gscale, cudaStream_t st) {
   if (B <= 0) return 0;
   k_sigmoid_logloss<<<pbx_grid_for(B, 256, 1), 256, 0, st>>>(logit, label, B, pred, loss_sum, dlogit, gscale);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
 int pbx_fm_fwd(const float* x, int ldx, int B, int S, int E, int wcol, int vcol, int D, float* fm, cudaStream_t st) {
   if (B <= 0) return 0;
   k_fm_fwd<<<pbx_grid_for((long long)B * 32, 256, 8), 256, 0, st>>>(x, ldx, B, S, E, wcol, vcol, D, fm);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
@@ -336,7 +336,7 @@ int pbx_fm_bwd(const float* x, int ldx, const float* g, int B, int S, int E, int
   if (B <= 0) return 0;
   k_fm_bwd<<<pbx_grid_for((long long)B * 32, 256, 8), 256, 0, st>>>(x, ldx, g, B, S, E, wcol, vcol, D, dx, lddx,
                                                                      accumulate);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
@@ -344,14 +344,14 @@ int pbx_cvm_fwd(const float* x, int64_t rows, int W, int use_cvm, float* y, cuda
   int64_t total = rows * (use_cvm ? W : W - 2);
   if (total <= 0) return 0;
   k_cvm_fwd<<<pbx_grid_for(total, 256, 8), 256, 0, st>>>(x, rows, W, use_cvm, y);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
 int pbx_cvm_bwd(const float* dy, const float* cvm, int64_t rows, int W, int use_cvm, float* dx, cudaStream_t st) {
   if (rows * W <= 0) return 0;
   k_cvm_bwd<<<pbx_grid_for(rows * W, 256, 8), 256, 0, st>>>(dy, cvm, rows, W, use_cvm, dx);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
@@ -359,7 +359,7 @@ int pbx_data_norm_fwd(const float* x, int64_t rows, int C, const float* bsize, c
                       float* y, float* means, float* scales, cudaStream_t st) {
   if (rows * C <= 0) return 0;
   k_data_norm_fwd<<<pbx_grid_for(rows * C, 256, 8), 256, 0, st>>>(x, rows, C, bsize, bsum, bsq, y, means, scales);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
@@ -372,7 +372,7 @@ int pbx_data_norm_bwd(const float* x, const float* dy, int64_t rows, int C, cons
   if (gy < 1) gy = 1;
   k_data_norm_bwd<<<dim3((C + 31) / 32, gy), 256, 0, st>>>(x, dy, rows, C, means, scales, eps, dx, d_size, d_sum,
                                                            d_sq);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
@@ -380,20 +380,20 @@ int pbx_auc_bucket(const float* pred, const float* label, const float* mask, int
                    double* sums, cudaStream_t st) {
   if (n <= 0) return 0;
   k_auc_bucket<<<pbx_grid_for(n, 256, 2), 256, 0, st>>>(pred, label, mask, n, nbuckets, table, sums);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
 int pbx_row_gather(const float* table, const int64_t* idx, int64_t n, int dim, float* out, cudaStream_t st) {
   if (n * dim <= 0) return 0;
   k_row_gather<<<pbx_grid_for(n * dim, 256, 8), 256, 0, st>>>(table, idx, n, dim, out);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
 int pbx_l2_flush(void* buf, int64_t bytes, cudaStream_t st) {
   k_fill_u32<<<pbx_grid_for(bytes / 4, 256, 8), 256, 0, st>>>((uint32_t*)buf, bytes / 4, 0u);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 

@@ -364,7 +364,7 @@ int launch_tc(const __nv_bfloat16* A, int lda, const __nv_bfloat16* B, int ldb, 
   }
   dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, splitk);
   k_gemm_tcgen05<BN><<<grid, GEMM_THREADS, SmemLayout<BN>::TOTAL, st>>>(ma, mb, M, N, K, kb_per, ep);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
@@ -396,7 +396,7 @@ int pbx_gemm_bf16_tn(const void* A, int lda, const void* B, int ldb, int M, int 
     dim3 grid((N + 15) / 16, (M + 15) / 16);
     k_gemm_simt<<<grid, dim3(16, 16), 0, st>>>((const __nv_bfloat16*)A, lda, (const __nv_bfloat16*)B, ldb, M, N, K,
                                                ep);
-    PBX_CUDA_CHECK(cudaGetLastError());
+    PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
     return 0;
   }
   PBX_REQUIRE(((uintptr_t)A & 15) == 0 && ((uintptr_t)B & 15) == 0 && (lda & 7) == 0 && (ldb & 7) == 0,

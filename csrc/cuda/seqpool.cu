@@ -175,7 +175,7 @@ int pbx_seqpool_cvm_fwd(const PbxSeqpoolParams* p, const float* d_x, const uint3
   int64_t total = (int64_t)p->S * p->B * p->concat * p->hidden;
   if (total == 0) return 0;
   k_seqpool_cvm_fwd<<<pbx_grid_for(total, 256, 16), 256, 0, st>>>(*p, d_x, d_restore, d_lod, d_out);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
@@ -184,7 +184,7 @@ int pbx_seqpool_cvm_bwd(const PbxSeqpoolParams* p, const float* d_dout, const fl
   int64_t total = (int64_t)p->S * p->B * p->hidden;
   if (total == 0) return 0;
   k_seqpool_cvm_bwd<<<pbx_grid_for(total, 256, 16), 256, 0, st>>>(*p, d_dout, d_cvm, d_lod, d_dx, dx_stride);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
@@ -194,14 +194,14 @@ int pbx_pull_scatter(const float* d_vals, int vstride, const uint32_t* d_restore
   if (total <= 0) return 0;
   k_pull_scatter<<<pbx_grid_for(total, 256, 16), 256, 0, st>>>(d_vals, vstride, d_restore, n, hidden, skip,
                                                                 scale_embedx, d_out);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
 int pbx_key2slot(const int32_t* d_lod, int B, int S, int64_t n, int32_t* d_out, cudaStream_t st) {
   if (n <= 0) return 0;
   k_key2slot<<<pbx_grid_for(n, 256, 16), 256, 0, st>>>(d_lod, B, S, n, d_out);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 

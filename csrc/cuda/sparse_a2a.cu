@@ -497,6 +497,7 @@ int pbx_sparse_pull(void* hnd, const uint64_t* d_keys, int64_t n, uint32_t* d_re
   void* kargs[] = {(void*)&dctx, (void*)&nvr, (void*)&args};
   PBX_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_sparse_pull<false>, dim3(c->grid_blocks),
                                              dim3(PBX_A2A_THREADS), kargs, 0, st));
+  pbx_note_launch(1);
   return 0;
 }
 
@@ -533,6 +534,7 @@ int pbx_sparse_push(void* hnd, const uint32_t* d_restore, int64_t n, const float
   void* kargs[] = {(void*)&dctx, (void*)&nvr, (void*)&args};
   PBX_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_sparse_push<false>, dim3(c->grid_blocks),
                                              dim3(PBX_A2A_THREADS), kargs, 0, st));
+  pbx_note_launch(1);
   return 0;
 }
 

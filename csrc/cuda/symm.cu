@@ -227,6 +227,7 @@ int pbx_symm_collective(void* h, int64_t off, int64_t n, float scale, int op, in
   int nvr = 1;
   void* args[] = {(void*)&d, (void*)&nvr, (void*)&off, (void*)&n, (void*)&scale, (void*)&op, (void*)&root};
   PBX_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_symm_collective<false>, dim3(blocks), dim3(512), args, 0, st));
+  pbx_note_launch(1);
   return 0;
 }
 

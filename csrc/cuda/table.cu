@@ -18,6 +18,11 @@ void pbx_set_error(const char* fmt, ...) {
   g_err = buf;
 }
 
+#include <atomic>
+static std::atomic<long long> g_launches{0};
+extern "C" long long pbx_launch_count() { return g_launches.load(); }
+void pbx_note_launch(int n) { g_launches += n; }
+
 namespace {
 
 __global__ void k_fill_keys(uint64_t* keys, uint64_t n) {
@@ -221,7 +226,7 @@ int pbx_table_create(void** out, uint64_t capacity, int embedx_dim, int optimize
   PBX_CUDA_CHECK(cudaMemset(t->view.dirty, 0, capacity));
   PBX_CUDA_CHECK(cudaMemset(t->d_counter, 0, 2 * sizeof(unsigned long long)));
   k_fill_keys<<<pbx_grid_for((long long)capacity, 256), 256>>>(t->view.keys, capacity);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   PBX_CUDA_CHECK(cudaDeviceSynchronize());
   *out = t;
   return 0;
@@ -256,7 +261,7 @@ int pbx_table_set_test_mode(void* h, int on) {
 int pbx_table_clear(void* h, cudaStream_t st) {
   PbxTable* t = (PbxTable*)h;
   k_fill_keys<<<pbx_grid_for((long long)t->view.capacity, 256), 256, 0, st>>>(t->view.keys, t->view.capacity);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   PBX_CUDA_CHECK(cudaMemsetAsync(t->view.dirty, 0, t->view.capacity, st));
   return 0;
 }
@@ -268,7 +273,7 @@ int pbx_table_insert(void* h, const uint64_t* d_keys, int64_t n, const float* d_
   int* status = (int*)(t->d_counter + 1);
   PBX_CUDA_CHECK(cudaMemsetAsync(status, 0, sizeof(int), st));
   k_insert<<<pbx_grid_for(n, 256), 256, 0, st>>>(t->view, d_keys, n, d_rows, status);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   int hs = 0;
   PBX_CUDA_CHECK(cudaMemcpyAsync(&hs, status, sizeof(int), cudaMemcpyDeviceToHost, st));
   PBX_CUDA_CHECK(cudaStreamSynchronize(st));
@@ -283,7 +288,7 @@ int pbx_table_fill_synthetic(void* h, uint64_t n_total, uint64_t key_seed, int r
   PBX_CUDA_CHECK(cudaMemsetAsync(status, 0, sizeof(int), st));
   k_fill_synth<<<pbx_grid_for((long long)n_total, 256, 16), 256, 0, st>>>(t->view, n_total, key_seed, rank, nranks,
                                                                             create_mf, status);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   int hs = 0;
   PBX_CUDA_CHECK(cudaMemcpyAsync(&hs, status, sizeof(int), cudaMemcpyDeviceToHost, st));
   PBX_CUDA_CHECK(cudaStreamSynchronize(st));
@@ -295,7 +300,7 @@ int pbx_table_count(void* h, int64_t* out, cudaStream_t st) {
   PbxTable* t = (PbxTable*)h;
   PBX_CUDA_CHECK(cudaMemsetAsync(t->d_counter, 0, sizeof(unsigned long long), st));
   k_count<<<pbx_grid_for((long long)t->view.capacity, 256), 256, 0, st>>>(t->view, t->d_counter);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   unsigned long long v = 0;
   PBX_CUDA_CHECK(cudaMemcpyAsync(&v, t->d_counter, sizeof(v), cudaMemcpyDeviceToHost, st));
   PBX_CUDA_CHECK(cudaStreamSynchronize(st));
@@ -311,7 +316,7 @@ int pbx_table_dump(void* h, uint64_t* d_keys_out, float* d_rows_out, int64_t max
   PBX_CUDA_CHECK(cudaMemsetAsync(t->d_counter, 0, sizeof(unsigned long long), st));
   k_dump<<<pbx_grid_for((long long)t->view.capacity, 256), 256, 0, st>>>(
       t->view, d_keys_out, d_rows_out, (unsigned long long)max_n, t->d_counter, mode, clear_dirty);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   unsigned long long v = 0;
   PBX_CUDA_CHECK(cudaMemcpyAsync(&v, t->d_counter, sizeof(v), cudaMemcpyDeviceToHost, st));
   PBX_CUDA_CHECK(cudaStreamSynchronize(st));
@@ -326,7 +331,7 @@ int pbx_table_lookup(void* h, const uint64_t* d_keys, int64_t n, float* d_out, i
   PBX_REQUIRE(out_stride >= 3 + t->view.L.embedx_dim, "lookup out_stride %d < hidden %d", out_stride,
               3 + t->view.L.embedx_dim);
   k_lookup<<<pbx_grid_for(n, 256), 256, 0, st>>>(t->view, d_keys, n, d_out, out_stride, d_rows_out);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
@@ -336,7 +341,7 @@ int pbx_table_update(void* h, const uint64_t* d_keys, const float* d_push, int p
   if (n <= 0 || t->view.test_mode) return 0;
   PBX_REQUIRE(push_stride >= 4 + t->view.L.embedx_dim, "push_stride %d too small", push_stride);
   k_update<<<pbx_grid_for(n, 128), 128, 0, st>>>(t->view, d_keys, d_push, push_stride, n);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
@@ -365,7 +370,7 @@ int pbx_table_shrink(void* h, float decay, float delete_threshold, float delete_
   PBX_CUDA_CHECK(cudaStreamSynchronize(st));
   pbx_table_clear(h, st);
   if (n) k_reinsert<<<pbx_grid_for((long long)n, 256), 256, 0, st>>>(t->view, tk, tr, td, n);
-  PBX_CUDA_CHECK(cudaGetLastError());
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   PBX_CUDA_CHECK(cudaStreamSynchronize(st));
   cudaFree(evict);
   cudaFree(tk);

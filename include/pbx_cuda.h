@@ -17,6 +17,8 @@ extern "C" {
 typedef void* pbx_stream_t;
 
 const char* pbx_last_error(void);
+/* number of kernel launches this library has issued in the calling process */
+long long pbx_launch_count(void);
 
 /* ---- sparse table shard (csrc/cuda/table.cu) --------------------------------
  * reference: heter_ps/hashtable.h, hashtable_kernel.cu:34-337, optimizer.cuh.h,
