@@ -1,0 +1,256 @@
+"""The remaining CTR operator family of the reference, expressed on PyTorch tensors.
+
+These ops are not on the hot path of the headline models; they are written as compositions
+of PyTorch ops (differentiable through autograd, CPU and CUDA), with the GEMM-shaped ones
+able to route through the tcgen05 kernel.  Each cites the reference op it restates.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from . import functional as F
+
+
+# ---------------------------------------------------------------- rank_attention
+def rank_attention(x: torch.Tensor, rank_offset: torch.Tensor, rank_param: torch.Tensor, max_rank: int = 3,
+                   max_size: int = 0) -> torch.Tensor:
+    """PV-aware attention over the ads of one page view.
+
+    ``rank_offset`` [N, 2*max_rank+1] int: col 0 = own rank (1-based, <= 0: invalid), then for
+    every k: (rank of the k-th ad of the same PV, row index of that ad).  ``rank_param``
+    [max_rank*max_rank*C, out]: one [C, out] block per (own rank, other rank) pair.
+    out[i] = sum_k x[idx_k] @ P[own-1, rank_k-1]  over valid k.
+    Reference: operators/rank_attention_op.cu:30-392, rank_attention.cu.h:28-195; numpy oracle
+    test_rank_attention_op.py:25-108."""
+    N_, Cc = x.shape
+    out_dim = rank_param.shape[1]
+    ro = rank_offset.long()
+    own = ro[:, 0] - 1                                   # [N]
+    faster = ro[:, 1::2] - 1                             # [N, max_rank]
+    index = ro[:, 2::2]                                  # [N, max_rank]
+    valid = (own[:, None] >= 0) & (faster >= 0)
+    xin = x[index.clamp(min=0)] * valid[..., None].to(x.dtype)        # [N, R, C]
+    blocks = rank_param.view(max_rank * max_rank, Cc, out_dim)
+    bid = (own.clamp(min=0)[:, None] * max_rank + faster.clamp(min=0))  # [N, R]
+    P = blocks[bid]                                                     # [N, R, C, out]
+    return torch.einsum("nrc,nrco->no", xin, P)
+
+
+def rank_attention2(x, rank_offset, rank_param, max_rank: int = 3):
+    """Same contract as ``rank_attention`` (the reference's second kernel variant)."""
+    return rank_attention(x, rank_offset, rank_param, max_rank)
+
+
+def build_rank_offset(search_id: torch.Tensor, rank: torch.Tensor, max_rank: int = 3) -> torch.Tensor:
+    """Rank-offset matrix of a PV-merged batch (reference CopyRankOffsetKernel /
+    GetRankOffset, data_feed.cu:1319-1369, data_feed.cc:3531-3591): rows of one ``search_id``
+    are one page view; ranks are 1-based, ranks > max_rank are ignored."""
+    n = search_id.numel()
+    out = torch.full((n, 2 * max_rank + 1), -1, dtype=torch.int32)
+    sid, rk = search_id.tolist(), rank.tolist()
+    groups: dict = {}
+    for i, s in enumerate(sid):
+        groups.setdefault(s, []).append(i)
+    for rows in groups.values():
+        for i in rows:
+            if not (1 <= rk[i] <= max_rank):
+                continue
+            out[i, 0] = rk[i]
+            for j in rows:
+                if 1 <= rk[j] <= max_rank:
+                    k = rk[j] - 1
+                    out[i, 2 * k + 1] = rk[j]
+                    out[i, 2 * k + 2] = j
+    return out
+
+
+# ---------------------------------------------------------------- batch_fc
+class BatchFC(nn.Module):
+    """``out[s] = x[s] @ W[s] + b[s]`` for every slot pair s (reference batch_fc,
+    operators/batch_fc_op.cu:34-567; oracle test_batch_fc_op.py:25)."""
+
+    def __init__(self, num: int, in_dim: int, out_dim: int, act: str | None = None):
+        super().__init__()
+        self.w = nn.Parameter(torch.randn(num, in_dim, out_dim) / in_dim ** 0.5)
+        self.b = nn.Parameter(torch.zeros(num, out_dim))
+        self.act = act
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return batch_fc(x, self.w, self.b, self.act)
+
+
+def batch_fc(x: torch.Tensor, w: torch.Tensor, b: torch.Tensor, act: str | None = None) -> torch.Tensor:
+    y = torch.baddbmm(b[:, None, :], x, w)
+    if act == "relu":
+        y = torch.relu(y)
+    return y
+
+
+# ---------------------------------------------------------------- scaled_fc
+def scaled_fc(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, input_scale_factor: float = 1.0,
+              bias_scale_factor: float = 1.0, grad_scale_factor: float = 1.0) -> torch.Tensor:
+    """fp16 GEMM with scaled input and bias: ``(x*s_in) @ w + bias*s_b`` computed in half
+    precision, result cast back to fp32 (reference scaled_fc_op.cu:39-342).  Here the operands
+    are rounded to bf16 and accumulated in fp32 — the tcgen05 kernel's native mode."""
+    class _Fn(torch.autograd.Function):
+        @staticmethod
+        def forward(ctx, x, w, bias):
+            ctx.save_for_backward(x, w)
+            xs = (x * input_scale_factor).to(torch.bfloat16).float()
+            ws = w.to(torch.bfloat16).float()
+            return xs @ ws + bias * bias_scale_factor
+
+        @staticmethod
+        def backward(ctx, g):
+            x, w = ctx.saved_tensors
+            g = g * grad_scale_factor
+            gb = g.to(torch.bfloat16).float()
+            dx = (gb @ w.to(torch.bfloat16).float().t()) * input_scale_factor / grad_scale_factor
+            dw = ((x * input_scale_factor).to(torch.bfloat16).float().t() @ gb) / grad_scale_factor
+            db = g.sum(0) * bias_scale_factor / grad_scale_factor
+            return dx, dw, db
+    return _Fn.apply(x, w, bias)
+
+
+def scaled_int8fc(x, w, bias, input_scale_factor=1.0, bias_scale_factor=1.0, weight_scale: float = 127.0):
+    """int8-weight variant (reference scaled_int8fc_op.cu:38-440): weights are quantised to
+    int8 with a symmetric scale, the product is de-quantised.  B200 tensor cores still have an
+    int8 path, but the CTR towers here keep bf16; this op simulates the quantisation."""
+    wmax = w.detach().abs().amax().clamp(min=1e-8)
+    wq = torch.round(w / wmax * weight_scale).clamp(-127, 127)
+    wdq = (wq * wmax / weight_scale).detach() + (w - w.detach())     # straight-through estimator
+    return (x * input_scale_factor) @ wdq + bias * bias_scale_factor
+
+
+# ---------------------------------------------------------------- cross_norm_hadamard
+class CrossNormHadamard(nn.Module):
+    """For ``fields_num`` field pairs (a_i, b_i) of width ``embed_dim`` laid side by side in the
+    input, emit ``[a_i, b_i, a_i*b_i]`` and normalise every output column with data_norm style
+    running summaries (reference cross_norm_hadamard.cu.h:44-240, cross_norm_hadamard_op.cu)."""
+
+    def __init__(self, fields_num: int, embed_dim: int, epsilon: float = 1e-4, summary_decay_rate: float = 0.9999999,
+                 sync_stats: bool = False):
+        super().__init__()
+        self.fields_num, self.embed_dim = fields_num, embed_dim
+        self.norm = F.DataNorm(fields_num * 3 * embed_dim, epsilon, summary_decay_rate, sync_stats,
+                               name="cross_norm")
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        B = x.shape[0]
+        f, d = self.fields_num, self.embed_dim
+        pairs = x.view(B, f, 2, d)
+        a, b = pairs[:, :, 0], pairs[:, :, 1]
+        y = torch.cat([a, b, a * b], dim=2).reshape(B, f * 3 * d)
+        return self.norm(y)
+
+
+# ---------------------------------------------------------------- concat / slice utilities
+def fused_concat(inputs, start_index: int = 0, length: int = -1, axis: int = 1) -> torch.Tensor:
+    """Column slice ``[start, start+length)`` of every input, concatenated (reference
+    fused_concat_op.cu:34-258)."""
+    outs = []
+    for t in inputs:
+        s = start_index if start_index >= 0 else t.shape[1] + start_index
+        e = t.shape[1] if length < 0 else s + length
+        outs.append(t[:, s:e])
+    return torch.cat(outs, dim=axis)
+
+
+def partial_concat(inputs, start_index: int = 0, length: int = -1) -> torch.Tensor:
+    """reference partial_concat op (operators/partial_concat_op.*)."""
+    return fused_concat(inputs, start_index, length, 1)
+
+
+def partial_sum(inputs, start_index: int = 0, length: int = -1) -> torch.Tensor:
+    """Sum of the same column slice of every input (operators/partial_sum_op.*)."""
+    s = start_index
+    outs = [t[:, s:(t.shape[1] if length < 0 else s + length)] for t in inputs]
+    return torch.stack(outs, 0).sum(0)
+
+
+def fused_seqpool_concat(pooled: torch.Tensor, num_slots: int, offsets=None, dims=None) -> torch.Tensor:
+    """Select ``dims[i]`` columns starting at ``offsets[i]`` from every slot block of a pooled
+    tensor [B, S*E] and concatenate (reference fused_seqpool_concat, fused_concat_op.cu)."""
+    E = pooled.shape[1] // num_slots
+    blocks = pooled.view(pooled.shape[0], num_slots, E)
+    if offsets is None:
+        return pooled
+    return torch.cat([blocks[:, :, o:o + d].reshape(pooled.shape[0], -1) for o, d in zip(offsets, dims)], 1)
+
+
+def fused_seq_tensor(x: torch.Tensor, ad_input: torch.Tensor, batch_count: int, max_length: int, slot_num: int,
+                     fea_emb_dim: int, ad_slot_num: int, ad_slot_offset: int = 0):
+    """DIN-style history tensor builder (reference fused_seq_tensor_op.cu:14-147): reshape the
+    user-behaviour embeddings ``x`` [ins*batch_count, slot_num*max_length*dim] into
+    (din_out [ins, batch_count*max_length, (slot_num + ad_slot_num)... ], mask, side info).
+    Returns ``(din, mask, side, ad_slot_session)`` with the ad slots broadcast along time."""
+    ins = x.shape[0] // batch_count
+    seq = x.view(ins, batch_count, slot_num, max_length, fea_emb_dim)
+    mask = (seq.abs().sum(dim=(2, 4)) > 0).to(x.dtype)                     # [ins, batch_count, max_length]
+    ad = ad_input.view(ins, batch_count, -1, fea_emb_dim)[:, :, ad_slot_offset:ad_slot_offset + ad_slot_num]
+    ad_b = ad[:, :, :, None, :].expand(ins, batch_count, ad_slot_num, max_length, fea_emb_dim)
+    din = torch.cat([seq[:, :, :ad_slot_num] if slot_num >= ad_slot_num else seq, ad_b], dim=2)
+    din = din.permute(0, 1, 3, 2, 4).reshape(ins, batch_count, max_length, -1)
+    side = seq[:, :, ad_slot_num:].permute(0, 1, 3, 2, 4).reshape(ins, batch_count, max_length, -1)
+    ad_sess = ad_b.permute(0, 1, 3, 2, 4).reshape(ins, batch_count, max_length, -1)
+    return din, mask, side, ad_sess
+
+
+def shuffle_batch(x: torch.Tensor, seed: int | None = None):
+    """Row permutation of a batch; returns (shuffled, index) (operators/shuffle_batch_op.*)."""
+    g = torch.Generator(device="cpu")
+    if seed is not None:
+        g.manual_seed(seed)
+    idx = torch.randperm(x.shape[0], generator=g).to(x.device)
+    return x[idx], idx
+
+
+def filter_by_instag(ins: torch.Tensor, ins_tag_lod, ins_tags: torch.Tensor, filter_tags, out_val_if_empty: float = 0.0):
+    """Keep the instances that carry at least one of ``filter_tags`` (reference
+    filter_by_instag_op.*): ``ins_tag_lod`` are the per-instance tag offsets into
+    ``ins_tags``.  Returns (kept rows, index map [kept, 2] = (new row, old row), loss weight)."""
+    want = set(int(t) for t in filter_tags)
+    tags = ins_tags.tolist()
+    keep = [i for i in range(len(ins_tag_lod) - 1)
+            if any(int(t) in want for t in tags[ins_tag_lod[i]:ins_tag_lod[i + 1]])]
+    if not keep:
+        out = torch.full((1, ins.shape[1]), out_val_if_empty, dtype=ins.dtype, device=ins.device)
+        return out, torch.zeros(1, 2, dtype=torch.int64), torch.zeros(1, 1, dtype=ins.dtype, device=ins.device)
+    idx = torch.tensor(keep, device=ins.device)
+    index_map = torch.stack([torch.arange(len(keep)), torch.tensor(keep)], 1)
+    return ins[idx], index_map, torch.ones(len(keep), 1, dtype=ins.dtype, device=ins.device)
+
+
+# ---------------------------------------------------------------- fused_seqpool_cvm_with_pcoc
+def fused_seqpool_cvm_with_pcoc(x: torch.Tensor, lod: torch.Tensor, batch_size: int, num_slots: int,
+                                pcoc_cvm: torch.Tensor | None = None, use_cvm: bool = True, cvm_offset: int = 7,
+                                pad_value: float = 0.0, need_filter: bool = False, show_coeff: float = 0.2,
+                                clk_coeff: float = 1.0, threshold: float = 0.96, quant_ratio: int = 0):
+    """PCOC variant: the value rows carry ``cvm_offset`` leading statistics columns — show,
+    click and ``pclk_num = (cvm_offset - 2)`` predicted-click sums; output cvm columns are
+    ``log(show+1), log(clk+1)-log(show+1)`` followed by
+    ``log(pclk_i+1) - log(show+1)`` ... calibrated per q-value bucket
+    (reference fused_seqpool_cvm_with_pcoc_op.cu:36-294).  Sum-pooling via segment sums."""
+    H = x.shape[1]
+    G = batch_size * num_slots
+    lens = (lod[1:] - lod[:-1]).long()
+    seg = torch.repeat_interleave(torch.arange(G, device=x.device), lens)
+    rows = x
+    if need_filter:
+        sc = (x[:, 0] - x[:, 1]) * show_coeff + x[:, 1] * clk_coeff
+        keep = ~(sc < threshold)
+        rows = x * keep[:, None].to(x.dtype)
+    emb = rows[:, cvm_offset:]
+    if quant_ratio > 0:
+        emb = torch.trunc(emb * quant_ratio + 0.5) / quant_ratio
+        rows = torch.cat([rows[:, :cvm_offset], emb], 1)
+    pooled = torch.zeros(G, H, dtype=x.dtype, device=x.device).index_add_(0, seg, rows) + pad_value
+    if use_cvm:
+        show = torch.log(pooled[:, 0:1] + 1)
+        stats = torch.log(pooled[:, 1:cvm_offset] + 1) - show
+        out = torch.cat([show, stats, pooled[:, cvm_offset:]], 1)
+    else:
+        out = pooled[:, cvm_offset:]
+    E = out.shape[1]
+    return out.view(num_slots, batch_size, E).permute(1, 0, 2).reshape(batch_size, num_slots * E)
