@@ -1,0 +1,105 @@
+/* paddlebox_b200 — C ABI of the host runtime (libpbx_host.so, csrc/host/*.cc).
+ * Every int function returns 0 on success; otherwise pbh_last_error() holds the reason.
+ * Reference citations are relative to the PaddleBox tree. */
+#ifndef PBX_HOST_H_
+#define PBX_HOST_H_
+#include <stdint.h>
+#include "pbx_types.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* pbh_last_error(void);
+
+/* ---- dataset / data feed (csrc/host/dataset.cc, api.cc) -----------------------------
+ * reference: PadBoxSlotDataset (framework/data_set.cc:1905-2828), SlotPaddleBoxDataFeed
+ * (framework/data_feed.cc:2993-4153), compute_batch_num (data_set.cc:280-331) */
+int pbh_dataset_create(void** out);
+int pbh_dataset_destroy(void* ds);
+int pbh_dataset_set_slots(void* ds, int n, const char* const* names, const int* types, const int* is_dense,
+                          const int* is_used, const int* dims);
+int pbh_dataset_set_filelist(void* ds, int n, const char* const* files);
+int pbh_dataset_set_int(void* ds, const char* key, int64_t v);
+int pbh_dataset_set_float(void* ds, const char* key, double v);
+int pbh_dataset_set_str(void* ds, const char* key, const char* v);
+int pbh_dataset_load_into_memory(void* ds);
+int pbh_dataset_preload_into_memory(void* ds);
+int pbh_dataset_wait_preload_done(void* ds);
+int pbh_dataset_release_memory(void* ds);
+int pbh_dataset_local_shuffle(void* ds, uint64_t seed);
+int pbh_dataset_slots_shuffle(void* ds, const int* slots, int n, uint64_t seed);
+int pbh_dataset_prepare_train(void* ds, int nworkers, int shuffle, uint64_t seed, int64_t min_batches);
+int64_t pbh_dataset_num_records(void* ds);
+int64_t pbh_dataset_num_batches(void* ds, int worker);
+int pbh_dataset_n_sparse(void* ds);
+int pbh_dataset_dense_dim(void* ds);
+int64_t pbh_dataset_total_feasigns(void* ds);
+int pbh_dataset_batch_shape(void* ds, int worker, int64_t b, int* B, int64_t* n_keys);
+int pbh_dataset_pack_batch(void* ds, int worker, int64_t b, uint64_t* keys, int32_t* off, float* dense,
+                           int slot_major);
+int pbh_dataset_batch_meta(void* ds, int worker, int64_t b, uint64_t* search_ids, uint32_t* ranks,
+                           uint32_t* cmatch);
+int64_t pbh_dataset_batch_ins_ids(void* ds, int worker, int64_t b, char* buf, int64_t cap);
+int64_t pbh_dataset_unique_keys(void* ds, uint64_t* out, int64_t max_n);
+int pbh_dataset_save_archive(void* ds, const char* path);
+int pbh_dataset_load_archive(void* ds, const char* path);
+int64_t pbh_dataset_stats(void* ds, char* buf, int64_t cap);
+int pbh_dataset_parse_line(void* ds, const char* line, int64_t* n_u64, int64_t* n_f32, uint64_t* u64_out,
+                           int64_t u64_cap, float* f32_out, int64_t f32_cap, uint64_t* search_id);
+int64_t pbh_compute_batch_ranges(int64_t ins_num, int batch_size, int nworkers, int64_t* starts, int* lens,
+                                 int64_t cap);
+
+/* parser plugin ABI (role of ISlotParser .so plugins, data_feed.cc:3604-3670): a plugin exports
+ *   int pbx_parse_line(const char* line, size_t len, void* ctx,
+ *                      void (*emit_u64)(void*, int slot, const uint64_t*, size_t),
+ *                      void (*emit_f32)(void*, int slot, const float*, size_t),
+ *                      void (*emit_meta)(void*, const char* ins_id, uint64_t search_id,
+ *                                        uint32_t rank, uint32_t cmatch));
+ * and returns 0 for a good line. */
+
+/* ---- host-memory table tier + CPU pull/push + checkpoints (csrc/host/host_table.cc) ----
+ * reference: libbox_ps memory tier, pscore MemorySparseTable::Save
+ * (distributed/ps/table/memory_sparse_table.cc:338-393), CtrDymfAccessor (ctr_dymf_accessor.cc) */
+int pbh_table_create(void** out, int embedx_dim, int optimizer, const PbxSparseOptConfig* cfg, uint64_t seed);
+int pbh_table_destroy(void* t);
+int64_t pbh_table_size(void* t);
+int pbh_table_set_config(void* t, const PbxSparseOptConfig* cfg);
+int pbh_table_set_test_mode(void* t, int on);
+int pbh_table_clear(void* t);
+int pbh_table_fetch_rows(void* t, const uint64_t* keys, int64_t n, float* out, int create);
+int pbh_table_store_rows(void* t, const uint64_t* keys, int64_t n, const float* rows, int mark_dirty);
+int pbh_table_pull(void* t, const uint64_t* keys, int64_t n, float* out, int out_stride);
+int pbh_table_push(void* t, const uint64_t* keys, int64_t n, const float* push, int push_stride);
+int64_t pbh_table_shrink(void* t, float decay, float delete_threshold, float delete_after_unseen_days);
+int pbh_table_save(void* t, const char* dir, int mode, int part_shard_base, float base_threshold,
+                   float delta_threshold, int clear_dirty, int64_t* n_saved);
+int pbh_table_load_file(void* t, const char* path, int serving, int64_t* n_loaded);
+int64_t pbh_table_keys(void* t, uint64_t* out, int64_t max_n);
+
+/* ---- AUC calculators (csrc/host/metrics.cc); reference fleet/metrics.cc:38-587 ---- */
+int pbh_auc_create(void** out, int table_size);
+int pbh_auc_destroy(void* a);
+int pbh_auc_reset(void* a);
+int pbh_auc_add(void* a, const float* pred, const float* label, const float* mask, int64_t n, int float_label);
+int pbh_auc_add_uid(void* a, const float* pred, const float* label, const uint64_t* uid, int64_t n);
+int pbh_auc_merge_tables(void* a, const double* tables, const double* sums);
+int pbh_auc_export(void* a, double* tables, double* sums);
+int pbh_auc_import(void* a, const double* tables, const double* sums);
+int pbh_auc_compute(void* a, double* out8);
+int pbh_auc_compute_wuauc(void* a, double* out4);
+int pbh_auc_nan_inf(void* a, double* out2);
+
+/* ---- async dense table (csrc/host/api.cc); reference boxps_worker.cc:61-370 ---- */
+int pbh_async_dense_create(void** out, int64_t n, float lr, int threads, int merge_limit);
+int pbh_async_dense_destroy(void* t);
+int pbh_async_dense_set_params(void* t, const float* p);
+int pbh_async_dense_pull(void* t, float* out);
+int pbh_async_dense_push(void* t, const float* g);
+int pbh_async_dense_wait(void* t);
+int64_t pbh_async_dense_updates(void* t);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PBX_HOST_H_ */
