@@ -8,6 +8,7 @@
 // CopyForTensorPadBoxKernel (data_feed.cu:1208-1384, data_feed.cc:3400-3522).
 #include "common.cuh"
 #include <cooperative_groups.h>
+#include <mutex>
 namespace cg = cooperative_groups;
 
 namespace {
@@ -108,6 +109,94 @@ int pbx_batch_build(const uint64_t* d_rec_keys, const int32_t* d_rec_off, int B,
   if (blocks < 1) blocks = 1;
   void* args[] = {(void*)&d_rec_keys, (void*)&d_rec_off, (void*)&B, (void*)&S, (void*)&d_keys_out,
                   (void*)&d_lod_out, (void*)&d_scratch};
+  PBX_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_batch_build, dim3(blocks), dim3(BB_THREADS), args, 0, st));
+  pbx_note_launch(1);
+  return 0;
+}
+
+}  // extern "C"
+
+// ---------------------------------------------------------------------------------------
+// Allocation-free variant.
+//
+// pbx_batch_build() needs a small device scratch array (one partial sum per thread block)
+// that its caller has to allocate.  Some callers are not in a position to allocate device
+// memory at all:
+//   * a data-feed thread that prepares the next batch while training kernels are in flight —
+//     cudaMalloc / cudaFree synchronise the whole device, so one call there stalls every
+//     stream of the training step;
+//   * a process whose HBM is already fully committed (the sparse table and the symmetric
+//     buffers are sized to fill the card), where a late allocation can simply fail;
+//   * a host application that embeds this library under a fixed memory budget and forbids
+//     allocator calls from the code it loads.
+// For them the scratch lives in the library image itself: a file-scope __device__ array that
+// every GPU which loads libpbx_cuda.so carries (2 KiB per GPU) until the process exits.
+//
+// The array's name is only a host-side handle in host code — handing it to a kernel as if it
+// were a pointer would make the kernel fault (or, where the GPU can reach host memory, scribble
+// somewhere unrelated).  The real device address is obtained once per device with
+// cudaGetSymbolAddress() while that device is current, and that address is what the kernel gets.
+#define PBX_BB_STATIC_SCRATCH_INTS 512                       /* 2 KiB */
+#define PBX_BB_STATIC_BAGS_PER_BLOCK (BB_THREADS * 4)         /* same blocking as pbx_batch_build */
+#define PBX_BB_STATIC_MAX_BAGS ((long long)PBX_BB_STATIC_SCRATCH_INTS * PBX_BB_STATIC_BAGS_PER_BLOCK)
+
+static __device__ __align__(256) int32_t g_bb_static_scratch[PBX_BB_STATIC_SCRATCH_INTS];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_bb_static_mu;
+int32_t* g_bb_static_ptr[kMaxDevices] = {nullptr};
+
+// Resolves (once per device) the device address of g_bb_static_scratch for the current device.
+int bb_static_scratch_for_current_device(int32_t** out) {
+  int dev = -1;
+  PBX_CUDA_CHECK(cudaGetDevice(&dev));
+  PBX_REQUIRE(dev >= 0 && dev < kMaxDevices, "pbx_batch_build_static: device ordinal %d not supported", dev);
+  std::lock_guard<std::mutex> lock(g_bb_static_mu);
+  if (g_bb_static_ptr[dev] == nullptr) {
+    int32_t* p = nullptr;
+    PBX_CUDA_CHECK(cudaGetSymbolAddress((void**)&p, g_bb_static_scratch));
+    PBX_REQUIRE(p != nullptr, "pbx_batch_build_static: cudaGetSymbolAddress returned a null address");
+    g_bb_static_ptr[dev] = p;
+  }
+  *out = g_bb_static_ptr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" {
+
+// Same result as pbx_batch_build(), without a caller-provided scratch buffer and without any
+// allocation (no cudaMalloc / cudaFree / allocating library routine) inside the call.
+//
+//   * Limit: B * S (instances x sparse slots) must not exceed 1,048,576
+//     (= 512 scratch words x 2048 bags per block); larger batches are rejected with an error
+//     and must use pbx_batch_build() with their own scratch.  The number of keys is not limited.
+//   * First call on each device: looks up the device address of the built-in scratch array
+//     (cudaGetSymbolAddress with that device current).  Make that first call ahead of time,
+//     before any stream capture is started on that device.
+//   * The scratch is shared by every call on the device and keeps whatever the previous call
+//     left in it.  Nothing in it has to start at zero: each thread block overwrites its own
+//     word before any block reads it, and words beyond the current grid are never read.
+//   * Because the array is shared, two calls that can overlap on the same GPU (different
+//     streams, or different host threads without ordering between their streams) race on it
+//     and corrupt each other's offsets.  Order such calls on one stream or with events.
+int pbx_batch_build_static(const uint64_t* d_rec_keys, const int32_t* d_rec_off, int B, int S,
+                           uint64_t* d_keys_out, int32_t* d_lod_out, cudaStream_t st) {
+  if (B <= 0 || S <= 0) return 0;
+  const long long G = (long long)S * B;
+  PBX_REQUIRE(G <= PBX_BB_STATIC_MAX_BAGS,
+              "pbx_batch_build_static: B*S = %lld exceeds the built-in scratch limit of %lld bags "
+              "(use pbx_batch_build with caller-provided scratch)", G, PBX_BB_STATIC_MAX_BAGS);
+  int32_t* scratch = nullptr;
+  int rc = bb_static_scratch_for_current_device(&scratch);
+  if (rc) return rc;
+  int blocks = (int)((G + PBX_BB_STATIC_BAGS_PER_BLOCK - 1) / PBX_BB_STATIC_BAGS_PER_BLOCK);
+  int sms = pbx_num_sms();
+  if (blocks > sms) blocks = sms;
+  if (blocks < 1) blocks = 1;   // blocks <= 512 = PBX_BB_STATIC_SCRATCH_INTS by the check above
+  void* args[] = {(void*)&d_rec_keys, (void*)&d_rec_off, (void*)&B, (void*)&S, (void*)&d_keys_out,
+                  (void*)&d_lod_out, (void*)&scratch};
   PBX_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_batch_build, dim3(blocks), dim3(BB_THREADS), args, 0, st));
   pbx_note_launch(1);
   return 0;

@@ -119,6 +119,18 @@ int pbx_l2_flush(void* buf, int64_t bytes, pbx_stream_t stream);
  * reference: data_feed.cu:1208-1384, data_feed.cc:3400-3522, :4896-4940 */
 int pbx_batch_build(const uint64_t* d_rec_keys, const int32_t* d_rec_off, int B, int S, uint64_t* d_keys_out,
                     int32_t* d_lod_out, int32_t* d_scratch, pbx_stream_t stream);
+/* Allocation-free variant of pbx_batch_build (this entry point has no counterpart in the
+ * reference).  For callers that cannot allocate device memory — a feed thread running beside
+ * in-flight training kernels (cudaMalloc/cudaFree synchronise the device), a process whose HBM
+ * is fully committed, or a host that forbids allocator calls from loaded code — the block-sum
+ * scratch is a 2 KiB __device__ array inside the library (held by every GPU that loads it until
+ * exit), so the call needs only its inputs and outputs and performs no allocation.
+ * Limit: B * S <= 1,048,576; larger batches are rejected with an error.  The first call on a
+ * device resolves the array's device address (cudaGetSymbolAddress) — make it before any stream
+ * capture.  All calls on a device share the array (contents persist between calls; nothing in it
+ * needs zeroing); calls that may overlap on the same GPU race and must be ordered by the caller. */
+int pbx_batch_build_static(const uint64_t* d_rec_keys, const int32_t* d_rec_off, int B, int S,
+                           uint64_t* d_keys_out, int32_t* d_lod_out, pbx_stream_t stream);
 
 /* ---- symmetric memory + dense collectives (csrc/cuda/symm.cu) ------------------
  * reference: boxps_worker.cc:1191-1258 (SyncParam), c_allreduce_x_op.cc:114-151,
