@@ -33,7 +33,7 @@ sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
 def parse_args():
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
-    p.add_argument("--steps", type=int, default=30)
+    p.add_argument("--steps", type=int, default=100)
     p.add_argument("--warmup", type=int, default=5)
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
     p.add_argument("--batch", type=int, default=4096, help="instances per GPU per step")
@@ -46,6 +46,7 @@ def parse_args():
     p.add_argument("--n-batches", type=int, default=8, help="distinct synthetic batches rotated through")
     p.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
     p.add_argument("--profile-stages", action="store_true")
+    p.add_argument("--no-graph", action="store_true", help="do not capture the step in a CUDA graph")
     return p.parse_args()
 
 
@@ -212,6 +213,25 @@ def main():
         if not args.no_flush:
             N.check(lib.pbx_l2_flush(N.ptr(flush_buf), C.c_int64(flush_buf.numel()), N.stream_ptr()))
 
+    # ------------------------------------------------ whole-step CUDA graph (launch-bound loop)
+    graphed, launches_per_step = False, None
+    if not args.no_graph and not args.profile_stages:
+        trainer.train_step(dev_batches[0])                 # allocate workspaces eagerly first
+        torch.cuda.synchronize()
+        c0 = lib.pbx_launch_count()
+        trainer._eager_step(dev_batches[0])
+        launches_per_step = lib.pbx_launch_count() - c0
+        barrier()
+        graphed = trainer.enable_cuda_graph(dev_batches[0], max_keys)
+        if world > 1:   # every rank must take the same path (the collectives are inside the step)
+            flag = torch.tensor([1 if graphed else 0], device=dev)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            if int(flag) == 0 and graphed:
+                trainer._graph = None
+                graphed = False
+        if not graphed and rank == 0:
+            print("cuda graph capture unavailable:", getattr(trainer, "_graph_error", "?"), file=sys.stderr)
+
     # ------------------------------------------------ device-timed steps (inputs resident)
     for i in range(args.warmup):
         trainer.train_step(dev_batches[i % len(dev_batches)])
@@ -233,6 +253,8 @@ def main():
     barrier()
     wall = time.time() - wall0
     launches = lib.pbx_launch_count() - launches0 - (0 if args.no_flush else args.steps)
+    if graphed:   # launches replayed from the graph are not seen by the host-side counter
+        launches = launches_per_step * args.steps
     dev_ms = sum(a.elapsed_time(b) for a, b in evs)
     box.engine.check_status()
     loss_val = float(loss)
@@ -282,7 +304,7 @@ def main():
                        "dense_optimizer": "adam", "table_dtype": "fp32", "tower_dtype": "bf16 (fp32 accumulate)",
                        "l2": "flushed between timed steps (256 MB write)" if not args.no_flush else
                              "not flushed; table (>= 14 GB/GPU) and rotating batches exceed L2",
-                       "table_fill_s": round(fill_s, 2)},
+                       "table_fill_s": round(fill_s, 2), "cuda_graph": bool(graphed)},
             "e2e": {"value": round(e2e, 1), "unit": "instances/s", "ms_per_step": round(e2e_ms / args.steps, 4),
                     "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": 4},
             "gpu_launches": int(launches),

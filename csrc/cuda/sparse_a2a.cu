@@ -29,6 +29,8 @@ struct PbxPullArgs {
   const uint64_t* keys;
   int64_t n;
   uint32_t* restore;  // [n] out: unique-value row of every occurrence
+  const int32_t* n_dev;  // optional: the key count lives on the device (lod[S*B]); lets one
+                         // captured CUDA graph serve batches of different lengths
 };
 struct PbxPullArgsN { PbxPullArgs a[PBX_MAX_RANKS]; };
 
@@ -81,7 +83,8 @@ k_sparse_pull(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPullArgsN args)
   const int vr = blockIdx.x / bpr;
   const int lb = blockIdx.x % bpr;
   const PbxSparseDev& c = ctxs[vr];
-  const PbxPullArgs a = args.a[vr];
+  PbxPullArgs a = args.a[vr];
+  if (a.n_dev) a.n = (int64_t)__ldg(a.n_dev);
   const int R = c.nranks;
   const uint32_t cap = c.cap;
   const int tid = threadIdx.x;
@@ -481,7 +484,15 @@ int pbx_sparse_status(void* hnd, int* status, int reset, cudaStream_t st) {
   return 0;
 }
 
+// d_n (optional): device int32 holding the number of keys; when given, `n` is only the upper
+// bound used for validation and the kernel reads the real count from the device.
+int pbx_sparse_pull_ex(void* hnd, const uint64_t* d_keys, int64_t n, const int32_t* d_n, uint32_t* d_restore,
+                       cudaStream_t st);
 int pbx_sparse_pull(void* hnd, const uint64_t* d_keys, int64_t n, uint32_t* d_restore, cudaStream_t st) {
+  return pbx_sparse_pull_ex(hnd, d_keys, n, nullptr, d_restore, st);
+}
+int pbx_sparse_pull_ex(void* hnd, const uint64_t* d_keys, int64_t n, const int32_t* d_n, uint32_t* d_restore,
+                       cudaStream_t st) {
   PbxSparseCtx* c = (PbxSparseCtx*)hnd;
   PBX_REQUIRE(n <= c->max_keys, "batch has %lld keys, engine was sized for %lld", (long long)n,
               (long long)c->max_keys);
@@ -492,6 +503,7 @@ int pbx_sparse_pull(void* hnd, const uint64_t* d_keys, int64_t n, uint32_t* d_re
   args.a[0].keys = d_keys;
   args.a[0].n = n;
   args.a[0].restore = d_restore;
+  args.a[0].n_dev = d_n;
   const PbxSparseDev* dctx = c->d;
   int nvr = 1;
   void* kargs[] = {(void*)&dctx, (void*)&nvr, (void*)&args};

@@ -56,6 +56,9 @@ int pbx_sparse_geometry(void* ctx, int64_t* cap, int64_t* n_unique_rows, int* pu
 float* pbx_sparse_pull_values(void* ctx);
 int pbx_sparse_status(void* ctx, int* status, int reset, pbx_stream_t stream);
 int pbx_sparse_pull(void* ctx, const uint64_t* d_keys, int64_t n, uint32_t* d_restore, pbx_stream_t stream);
+/* d_n: optional device int32 with the real key count (n is then the upper bound) — graph-replay friendly */
+int pbx_sparse_pull_ex(void* ctx, const uint64_t* d_keys, int64_t n, const int32_t* d_n, uint32_t* d_restore,
+                       pbx_stream_t stream);
 int pbx_sparse_push(void* ctx, const uint32_t* d_restore, int64_t n, const float* d_dout, const float* d_cvm,
                     const int32_t* d_lod, int B, int S, int Eo, int cvm_offset, int dim_off, const float* d_gkeys,
                     const int32_t* d_key2slot, int hidden, int mode, float grad_scale, pbx_stream_t stream);

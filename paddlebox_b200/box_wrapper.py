@@ -224,11 +224,11 @@ class BoxWrapper:
         self.timers.add("end_pass", time.time() - t0)
 
     # ---- pull / push (single call; autograd wrappers live in ops/pull_box_sparse.py) ----------
-    def pull_sparse(self, keys: torch.Tensor) -> tuple:
+    def pull_sparse(self, keys: torch.Tensor, n_dev: torch.Tensor | None = None) -> tuple:
         """Returns (values [U or N, >= hidden], restore int32 [N]); occurrence i's record is
         ``values[restore[i], :hidden]``."""
         if self.use_cuda:
-            restore = self.engine.pull(keys)
+            restore = self.engine.pull(keys, n_dev=n_dev)
             return self.engine.values, restore
         uk, inv = torch.unique(keys, return_inverse=True)
         vals = self.host_table.pull(uk.numpy())

@@ -41,6 +41,8 @@ class SlotBatch:
     n_keys: int | None = None             # host-known N (avoids a sync); None -> keys.numel()
     ins_ids: list | None = None
     meta: dict | None = None              # search_id / rank / cmatch tensors
+    n_dev: torch.Tensor | None = None     # int32 device scalar with the real key count (static-shape
+                                          # batches replayed from a CUDA graph); usually lod[S*B:]
 
     @property
     def N(self) -> int:
@@ -79,7 +81,7 @@ class _PullBoxSparse(torch.autograd.Function):
     @staticmethod
     def forward(ctx, anchor, box, batch, size, offset):
         keys = batch.keys
-        vals, restore = box.pull_sparse(keys)
+        vals, restore = box.pull_sparse(keys, batch.n_dev)
         n = batch.N
         hidden = box.hidden
         width = size - 0
@@ -145,7 +147,7 @@ class _SparseEmbeddingPool(torch.autograd.Function):
     @staticmethod
     def forward(ctx, anchor, box, batch, cvm, attrs):
         B, S = batch.batch_size, batch.num_slots
-        vals, restore = box.pull_sparse(batch.keys)
+        vals, restore = box.pull_sparse(batch.keys, batch.n_dev)
         out = seqpool_cvm_forward(vals, batch.lod, B, S, attrs, box.hidden, restore=restore)
         ctx.box, ctx.batch, ctx.attrs, ctx.restore = box, batch, attrs, restore
         ctx.save_for_backward(cvm)

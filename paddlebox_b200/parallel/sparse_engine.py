@@ -79,14 +79,19 @@ class SparseEngine:
         """[nranks*cap, pull_stride] unique value rows of the last pull (row = restore idx)."""
         return self._values
 
-    def pull(self, keys: torch.Tensor, restore: torch.Tensor | None = None) -> torch.Tensor:
+    def pull(self, keys: torch.Tensor, restore: torch.Tensor | None = None,
+             n_dev: torch.Tensor | None = None) -> torch.Tensor:
         """Pull the value rows of ``keys`` (int64, device).  Returns the restore index
-        (int32 [n]): occurrence i's values are ``self.values[restore[i]]``."""
+        (int32 [n]): occurrence i's values are ``self.values[restore[i]]``.
+
+        ``n_dev`` (int32 device scalar, e.g. ``lod[S*B:]``): the real key count, read by the
+        kernel; ``keys`` may then be a fixed-capacity buffer — this is what lets one captured
+        CUDA graph serve batches of different lengths."""
         n = keys.numel()
         if restore is None:
             restore = torch.empty(max(n, 1), dtype=torch.int32, device=keys.device)
-        N.check(N.cuda().pbx_sparse_pull(self._h, N.ptr(keys), C.c_int64(n), N.ptr(restore), N.stream_ptr()),
-                "pbx_sparse_pull")
+        N.check(N.cuda().pbx_sparse_pull_ex(self._h, N.ptr(keys), C.c_int64(n), N.ptr(n_dev), N.ptr(restore),
+                                            N.stream_ptr()), "pbx_sparse_pull")
         return restore[:n]
 
     def push_pooled(self, restore: torch.Tensor, dout: torch.Tensor, cvm: torch.Tensor, lod: torch.Tensor, B: int,

@@ -75,10 +75,73 @@ class CTRTrainer:
         dist.all_reduce(stats, group=self.store.group)
         return stats / self.world
 
+    # ---- CUDA-graph replay of the whole step -----------------------------------------------
+    def enable_cuda_graph(self, example_batch, max_keys: int | None = None, warmup: int = 3) -> bool:
+        """Capture forward + backward/push + dense sync + optimizer of one step into a CUDA graph
+        and replay it for every later batch of the same (B, S, dense width).
+
+        Variable-length batches work because every buffer has a fixed capacity and the kernels
+        read the real key count from the device (``lod[S*B]``).  The ``warmup`` eager steps and
+        the capture run are real training steps on ``example_batch``.  Returns False (and stays
+        eager) when capture is not possible on this setup."""
+        if not example_batch.keys.is_cuda or self.cfg.is_test or self.sync.mode == "async":
+            return False
+        from .ops.pull_box_sparse import SlotBatch
+        B, S = example_batch.batch_size, example_batch.num_slots
+        dev = example_batch.keys.device
+        cap = int(max_keys or self.box.max_keys_per_batch)
+        keys = torch.zeros(cap, dtype=torch.int64, device=dev)
+        lod = torch.zeros(S * B + 1, dtype=torch.int32, device=dev)
+        dense = torch.zeros_like(example_batch.dense) if example_batch.dense is not None else None
+        static = SlotBatch(keys, lod, B, S, dense, n_keys=cap, n_dev=lod[S * B:])
+        self._static = static
+        self._copy_into_static(example_batch)
+        try:
+            side = torch.cuda.Stream(device=dev)
+            side.wait_stream(torch.cuda.current_stream(dev))
+            with torch.cuda.stream(side):
+                for _ in range(max(1, warmup)):
+                    self._eager_step(static)
+            torch.cuda.current_stream(dev).wait_stream(side)
+            torch.cuda.synchronize(dev)
+            self.store.mark_dirty()
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g):
+                loss = self._eager_step(static)
+            self._graph, self._graph_loss = g, loss
+            torch.cuda.synchronize(dev)
+            return True
+        except Exception as e:  # capture unsupported (e.g. cooperative launch in capture): stay eager
+            self._graph = None
+            self._graph_error = repr(e)
+            torch.cuda.synchronize(dev)
+            return False
+
+    def _copy_into_static(self, batch) -> None:
+        st = self._static
+        n = batch.N
+        if n > st.keys.numel():
+            raise ValueError(f"batch has {n} keys; the captured graph was sized for {st.keys.numel()}")
+        st.keys[:n].copy_(batch.keys[:n], non_blocking=True)
+        st.lod.copy_(batch.lod, non_blocking=True)
+        if st.dense is not None:
+            st.dense.copy_(batch.dense, non_blocking=True)
+        st.ins_ids = batch.ins_ids
+
     # ---- one mini-batch ------------------------------------------------------------------
     def train_step(self, batch) -> torch.Tensor:
         """forward + backward (= sparse push) + dense sync/update.  Returns the loss tensor
         (device; reading it is the caller's sync point)."""
+        g = getattr(self, "_graph", None)
+        if g is not None and not self.cfg.is_test and batch.batch_size == self._static.batch_size \
+                and batch.num_slots == self._static.num_slots:
+            self._copy_into_static(batch)
+            g.replay()
+            self.steps += 1
+            return self._graph_loss
+        return self._eager_step(batch)
+
+    def _eager_step(self, batch) -> torch.Tensor:
         t = self.timers
         self.sync.before_forward()
         with t.span("forward"):

@@ -1,0 +1,203 @@
+"""Worker functions for the multi-process tests (spawned with torch.multiprocessing)."""
+import os
+import traceback
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def _init(rank, world, port, backend):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    os.environ["RANK"] = str(rank)
+    os.environ["WORLD_SIZE"] = str(world)
+    if backend == "nccl":
+        torch.cuda.set_device(rank)
+        dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    else:
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+
+
+def run(fn, rank, world, port, backend, q, *args):
+    try:
+        _init(rank, world, port, backend)
+        out = fn(rank, world, *args)
+        q.put((rank, "ok", out))
+    except Exception:
+        q.put((rank, "error", traceback.format_exc()))
+    finally:
+        if dist.is_initialized():
+            dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------- CPU / gloo
+def cpu_feed_pass_and_dense(rank, world):
+    from paddlebox_b200.box_wrapper import BoxWrapper, owner_of
+    from paddlebox_b200.metrics import create_metric
+    from paddlebox_b200.parallel.dense import DenseOptimizer, DenseParamStore, DenseSync
+    box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=rank, world_size=world)
+    box.initialize_gpu_and_load_model({})
+    # every rank saw different keys; after the feed pass each rank holds exactly the keys it owns
+    mine = np.arange(rank * 100 + 1, rank * 100 + 181, dtype=np.uint64)
+    box.begin_feed_pass("20240101")
+    box.feed_pass(mine)
+    box.end_feed_pass()
+    allk = np.unique(np.concatenate([np.arange(r * 100 + 1, r * 100 + 181, dtype=np.uint64) for r in range(world)]
+                                    + [np.zeros(1, np.uint64)]))
+    expect = allk[owner_of(allk, world) == rank]
+    assert np.array_equal(box._pass_keys, expect), (len(box._pass_keys), len(expect))
+    # dense data parallel over gloo: grads averaged, replicas stay identical
+    torch.manual_seed(0)
+    model = torch.nn.Linear(8, 3)
+    store = DenseParamStore(model, rank, world)
+    opt = DenseOptimizer(store, lr=0.1, kind="sgd")
+    sync = DenseSync(store, opt, "allreduce")
+    x = torch.full((4, 8), float(rank + 1))
+    model(x).sum().backward()
+    g_local = store.gflat.clone()
+    sync.after_backward()
+    gathered = [torch.zeros_like(store.flat) for _ in range(world)]
+    dist.all_gather(gathered, store.flat)
+    assert all(torch.equal(gathered[0], t) for t in gathered)
+    # k-step averaging
+    sync2 = DenseSync(store, opt, "kstep", sync_weight_step=2)
+    for _ in range(2):
+        model(torch.randn(4, 8) * (rank + 1)).sum().backward()
+        sync2.after_backward()
+    dist.all_gather(gathered, store.flat)
+    assert all(torch.allclose(gathered[0], t) for t in gathered)
+    # ZeRO-1 sharding keeps replicas identical too
+    store.gflat.zero_()
+    sync3 = DenseSync(store, DenseOptimizer(store, lr=0.01, kind="adam"), "sharding")
+    model(torch.randn(4, 8)).sum().backward()
+    sync3.after_backward()
+    dist.all_gather(gathered, store.flat)
+    assert all(torch.allclose(gathered[0], t) for t in gathered)
+    # metric reduction: global AUC over both ranks' data
+    m = create_metric("AucCalculator", name="a", bucket_size=10000)
+    rs = np.random.RandomState(rank)
+    pred = torch.from_numpy(rs.rand(500).astype(np.float32))
+    label = (torch.from_numpy(rs.rand(500).astype(np.float32)) < pred).float()
+    m.add_data({"pred": pred, "label": label})
+    msg = m.get_metric_msg(dist.group.WORLD)
+    assert msg[7] == 500 * world
+    return msg[0]
+
+
+# ---------------------------------------------------------------- GPU / nccl + peer memory
+def gpu_sparse_and_dense(rank, world):
+    from paddlebox_b200.box_wrapper import BoxWrapper, owner_of
+    from paddlebox_b200.ops.sparse_table import SparseTable
+    from paddlebox_b200.parallel.symm import SymmetricBuffer
+    from paddlebox_b200.ops import reference as R
+    dev = torch.device("cuda", rank)
+    box = BoxWrapper.set_instance(embedx_dim=8, rank=rank, world_size=world)
+    box.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0, "mf_initial_range": 0.0},
+                                      table_capacity=1 << 14, max_keys_per_batch=1 << 13)
+    gen = torch.Generator().manual_seed(100 + rank)
+    B, S, H = 32, 4, 11
+    lens = torch.randint(0, 5, (S * B,), generator=gen)
+    lod = torch.zeros(S * B + 1, dtype=torch.int32)
+    lod[1:] = torch.cumsum(lens, 0)
+    keys = torch.randint(1, 800, (int(lod[-1]),), generator=gen, dtype=torch.int64)
+    box.begin_feed_pass("20240101")
+    box.feed_pass(keys)
+    box.end_feed_pass()
+    # give every owned key a recognisable value: embed_w = key % 97, show = 50
+    owned = box._pass_keys
+    rows = box.host_table.fetch_rows(owned, create=True)
+    rows[:, 0] = 50
+    rows[:, 2] = (owned % 97).astype(np.float32)
+    box.host_table.store_rows(owned, rows, mark_dirty=False)
+    box.begin_pass()
+    dk, dl = keys.to(dev), lod.to(dev)
+    vals, restore = box.pull_sparse(dk)
+    torch.cuda.synchronize()
+    box.engine.check_status()
+    got = vals[restore.long()][:, :H].cpu()
+    assert torch.equal(got[:, 2], (keys % 97).float()), "pulled embed_w does not match the owner's value"
+    assert torch.all(got[:, 0] == 50)
+    # push: show counts must arrive at the owners (sum over ranks)
+    dout = torch.zeros(B, S * H, device=dev)
+    cvm = torch.ones(B, 2, device=dev)
+    box.engine.push_pooled(restore, dout, cvm, dl, B, S, H, 2, 0, -float(B))
+    torch.cuda.synchronize()
+    box.engine.check_status()
+    dist.barrier()
+    box.end_pass()
+    # gather every rank's keys to compute the expected global show increments
+    all_keys = [None] * world
+    dist.all_gather_object(all_keys, keys.numpy())
+    cnt = {}
+    for ks in all_keys:
+        for k in ks.tolist():
+            cnt[k] = cnt.get(k, 0) + 1
+    rows2 = box.host_table.fetch_rows(owned, create=False)
+    for k, r in zip(owned.tolist(), rows2):
+        if k == 0:
+            continue
+        assert abs(r[0] - (50 + cnt.get(k, 0))) < 1e-4, (k, r[0], cnt.get(k, 0))
+    # symmetric-memory allreduce / reduce-scatter / all-gather / broadcast
+    n = 100003
+    buf = SymmetricBuffer(n, rank, world)
+    data = torch.arange(n, device=dev, dtype=torch.float32) * (rank + 1)
+    buf.tensor.copy_(data)
+    buf.allreduce(0, n, 1.0 / world)
+    torch.cuda.synchronize()
+    expect = torch.arange(n, device=dev, dtype=torch.float32) * sum(range(1, world + 1)) / world
+    assert torch.allclose(buf.tensor, expect, rtol=1e-6)
+    buf.tensor.fill_(float(rank))
+    buf.collective("broadcast", 0, n, root=world - 1)
+    torch.cuda.synchronize()
+    assert torch.all(buf.tensor == world - 1)
+    buf.check_status()
+    return True
+
+
+def gpu_deepfm_data_parallel(rank, world):
+    """Two data-parallel ranks: replicas stay bit-identical, loss decreases."""
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    from paddlebox_b200.models.ctr import DeepFM
+    from paddlebox_b200.ops.pull_box_sparse import SlotBatch
+    from paddlebox_b200.trainer import CTRTrainer, TrainerConfig
+    dev = torch.device("cuda", rank)
+    box = BoxWrapper.set_instance(embedx_dim=8, rank=rank, world_size=world)
+    box.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0}, table_capacity=1 << 14,
+                                      max_keys_per_batch=1 << 13)
+    gen = torch.Generator().manual_seed(7 + rank)
+    B, S = 64, 6
+    lens = torch.randint(1, 4, (S * B,), generator=gen)
+    lod = torch.zeros(S * B + 1, dtype=torch.int32)
+    lod[1:] = torch.cumsum(lens, 0)
+    keys = torch.randint(1, 300, (int(lod[-1]),), generator=gen, dtype=torch.int64)
+    dense = torch.rand(B, 4, generator=gen)
+    dense[:, 0] = (keys[lod[:B].long()] % 2).float()       # label depends on the first key of slot 0
+    box.begin_feed_pass("20240101")
+    box.feed_pass(keys)
+    box.end_feed_pass()
+    box.begin_pass()
+    torch.manual_seed(rank)    # different init on purpose: the trainer must broadcast rank 0's weights
+    model = DeepFM(num_slots=S, embedx_dim=8, dense_dim=3, hidden=(32, 16)).to(dev)
+    tr = CTRTrainer(model, box, TrainerConfig(dense_lr=1e-2))
+    batch = SlotBatch(keys.to(dev), lod.to(dev), B, S, dense.to(dev))
+    losses = [float(tr.train_step(batch).detach()) for _ in range(30)]
+    torch.cuda.synchronize()
+    box.engine.check_status()
+    gathered = [torch.zeros_like(tr.store.flat) for _ in range(world)]
+    dist.all_gather(gathered, tr.store.flat)
+    assert all(torch.equal(gathered[0], t) for t in gathered), "dense replicas diverged"
+    assert np.mean(losses[-5:]) < np.mean(losses[:5])
+    # the same step replayed from a CUDA graph keeps working across ranks
+    ok = tr.enable_cuda_graph(batch, 1 << 13)
+    flag = torch.tensor([1 if ok else 0], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if int(flag) == 0:
+        tr._graph = None
+    l2 = [float(tr.train_step(batch).detach()) for _ in range(5)]
+    torch.cuda.synchronize()
+    box.engine.check_status()
+    dist.all_gather(gathered, tr.store.flat)
+    assert all(torch.equal(gathered[0], t) for t in gathered)
+    box.end_pass()
+    return (losses[0], losses[-1], bool(int(flag)), l2[-1])
