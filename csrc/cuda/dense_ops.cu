@@ -292,8 +292,8 @@ int pbx_cast_transpose(const float* x, int ld, int M, int K, void* out_bf16, int
 
 int pbx_colsum_bf16(const void* x, int ld, int M, int N, float* out, cudaStream_t st) {
   if (M <= 0 || N <= 0) return 0;
-  int gy = (M + 255) / 256;
-  if (gy > 64) gy = 64;
+  int gy = (M + 63) / 64;   // 64 rows per block: short serial loops, plenty of blocks
+  if (gy > 128) gy = 128;
   k_colsum_bf16<<<dim3((N + 31) / 32, gy), 256, 0, st>>>((const __nv_bfloat16*)x, ld, M, N, out);
   PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;

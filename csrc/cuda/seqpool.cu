@@ -105,6 +105,49 @@ __global__ void k_seqpool_cvm_fwd(PbxSeqpoolParams p, const float* __restrict__ 
   }
 }
 
+// Fast path for the common configuration (base variant, cvm_offset 2, no filter / quant /
+// concat, 16-byte-aligned value rows): one thread per (bag, 4-column chunk), 128-bit gathers
+// of the value rows, CVM transform applied in the chunk that holds show/clk.
+__global__ void k_seqpool_cvm_fwd_fast(PbxSeqpoolParams p, const float* __restrict__ x,
+                                       const uint32_t* __restrict__ restore, const int32_t* __restrict__ lod,
+                                       float* __restrict__ out) {
+  const int H = p.hidden;
+  const int chunks = (H + 3) >> 2;
+  const int64_t total = (int64_t)p.S * p.B * chunks;
+  for (int64_t it = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; it < total;
+       it += (int64_t)gridDim.x * blockDim.x) {
+    const int ch = (int)(it % chunks);
+    const int64_t g = it / chunks;
+    const int s = (int)(g / p.B);
+    const int b = (int)(g % p.B);
+    const int32_t k0 = __ldg(lod + g), k1 = __ldg(lod + g + 1);
+    float4 acc = make_float4(p.pad_value, p.pad_value, p.pad_value, p.pad_value);
+    for (int32_t k = k0; k < k1; ++k) {
+      const uint32_t r = restore ? __ldg(restore + k) : (uint32_t)k;
+      const float4 v = *reinterpret_cast<const float4*>(x + (uint64_t)r * p.x_stride + ch * 4);
+      acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+    }
+    float v[4] = {acc.x, acc.y, acc.z, acc.w};
+    float* o = out + (int64_t)b * p.out_stride + (int64_t)s * p.Eo;
+    if (p.use_cvm) {
+      if (ch == 0) {
+        const float ls = logf(v[0] + 1.f);
+        v[1] = logf(v[1] + 1.f) - ls;
+        v[0] = ls;
+      }
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (ch * 4 + j < H) o[ch * 4 + j] = v[j];
+    } else {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int col = ch * 4 + j;
+        if (col >= 2 && col < H) o[col - 2] = v[j];
+      }
+    }
+  }
+}
+
 // dX[k, col] for every occurrence k: columns < cvm_offset come from the CVM input
 // (show / click labels), the others are dOut broadcast over the bag
 // (fused_seqpool_cvm_op.cu:814-1010; CPU twin fused_seqpool_cvm_op.cc:394-460).
@@ -174,6 +217,17 @@ int pbx_seqpool_cvm_fwd(const PbxSeqpoolParams* p, const float* d_x, const uint3
   PBX_REQUIRE(p->concat >= 1 && p->Eo % p->concat == 0, "bad embedx_concate_size");
   int64_t total = (int64_t)p->S * p->B * p->concat * p->hidden;
   if (total == 0) return 0;
+  const int chunks = (p->hidden + 3) / 4;
+  const bool fast = p->variant == 0 && p->cvm_offset == 2 && !p->clk_filter && !p->need_filter &&
+                    !p->embed_threshold_filter && p->quant_ratio == 0 && p->concat == 1 && !p->trade_w &&
+                    !p->slot_threshold && (p->x_stride & 3) == 0 && p->x_stride >= chunks * 4 &&
+                    ((uintptr_t)d_x & 15) == 0;
+  if (fast) {
+    int64_t items = (int64_t)p->S * p->B * chunks;
+    k_seqpool_cvm_fwd_fast<<<pbx_grid_for(items, 256, 16), 256, 0, st>>>(*p, d_x, d_restore, d_lod, d_out);
+    PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
+    return 0;
+  }
   k_seqpool_cvm_fwd<<<pbx_grid_for(total, 256, 16), 256, 0, st>>>(*p, d_x, d_restore, d_lod, d_out);
   PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;

@@ -42,6 +42,7 @@ struct PbxPushArgs {
   const float* cvm;         // [B, cvm_offset]  (show, click labels)
   const int32_t* lod;       // [S*B + 1] bag offsets, slot-major
   int B, S, Eo, cvm_offset, dim_off;
+  int ld_dout;              // words between rows of dout (>= S*Eo)
   // mode 1: explicit per-occurrence gradients [n, hidden] + slot of every occurrence
   const float* gkeys;
   const int32_t* key2slot;
@@ -234,7 +235,39 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
   grid.sync();
 
   // ---- Q1: merge by unique key (fused with the seqpool/CVM backward in mode 0)
-  if (a.mode == 0) {
+  if (a.mode == 0 && a.cvm_offset == 2) {
+    // one thread per (bag, 4-word chunk of the push record); chunks beyond the first are added
+    // with a single 16-byte vector reduction per occurrence
+    const int hidden = 3 + c.table.L.embedx_dim;
+    const int64_t items = (int64_t)a.S * a.B * pchunks;
+    for (int64_t it = gtid; it < items; it += gstride) {
+      const int ch = (int)(it % pchunks);
+      const int64_t g = it / pchunks;
+      const int s = (int)(g / a.B);
+      const int b = (int)(g % a.B);
+      const int32_t k0 = __ldg(a.lod + g), k1 = __ldg(a.lod + g + 1);
+      if (k0 >= k1) continue;
+      float v[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int col = ch * 4 + j - 1;  // push word w <-> value column w - 1
+        if (col < 0 || col >= hidden) v[j] = 0.f;
+        else if (col < 2) v[j] = __ldg(a.cvm + (int64_t)b * 2 + col);
+        else v[j] = a.grad_scale * __ldg(a.dout + (int64_t)b * a.ld_dout + (int64_t)s * a.Eo + (col - a.dim_off));
+      }
+      for (int32_t k = k0; k < k1; ++k) {
+        float* rec = c.push_acc + (uint64_t)__ldg(a.restore + k) * PD + ch * 4;
+        if (ch == 0) {
+          rec[0] = (float)s;
+          atomicAdd(rec + 1, v[1]);
+          atomicAdd(rec + 2, v[2]);
+          atomicAdd(rec + 3, v[3]);
+        } else {
+          pbx_red_add_v4(rec, v[0], v[1], v[2], v[3]);
+        }
+      }
+    }
+  } else if (a.mode == 0) {
     const int hidden = 3 + c.table.L.embedx_dim;
     const int64_t items = (int64_t)a.S * a.B * hidden;
     for (int64_t it = gtid; it < items; it += gstride) {
@@ -246,7 +279,7 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
       if (k0 >= k1) continue;
       float v;
       if (col < a.cvm_offset) v = a.cvm[(int64_t)b * a.cvm_offset + col];
-      else v = a.grad_scale * a.dout[(int64_t)b * a.S * a.Eo + (int64_t)s * a.Eo + (col - a.dim_off)];
+      else v = a.grad_scale * a.dout[(int64_t)b * a.ld_dout + (int64_t)s * a.Eo + (col - a.dim_off)];
       for (int32_t k = k0; k < k1; ++k) {
         float* rec = c.push_acc + (uint64_t)a.restore[k] * PD;
         atomicAdd(rec + col + 1, v);
@@ -270,6 +303,7 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
 
   // ---- Q2: ship merged records to their owners
   for (int o = 0; o < R; ++o) {
+    if (o == c.rank) continue;  // records for the local shard are applied straight from push_acc
     const int64_t items = (int64_t)c.send_cnt[o] * pchunks;
     const float4* src = reinterpret_cast<const float4*>(c.push_acc + (uint64_t)o * cap * PD);
     float4* dst = reinterpret_cast<float4*>(c.push_mail[o] + (uint64_t)c.rank * cap * PD);  // remote
@@ -283,14 +317,15 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
   for (int s = 0; s < R; ++s) {
     const uint32_t cnt = c.serve_cnt[s];
     if (!c.table.test_mode) {
-      const float* pm = c.push_mail[c.rank] + (uint64_t)s * cap * PD;
+      const float* pm = s == c.rank ? c.push_acc + (uint64_t)s * cap * PD
+                                    : c.push_mail[c.rank] + (uint64_t)s * cap * PD;
       const uint32_t* mrow = c.mail_row + (uint64_t)s * cap;
       for (int64_t j = gtid; j < (int64_t)cnt; j += gstride) {
         uint32_t row = mrow[j];
         if (row == PBX_NO_ROW) continue;
         // the key comes from the table itself: a faster peer may already be overwriting
         // this rank's key mailbox with the next batch
-        pbx_apply_push(c.table, row, c.table.keys[row], pm + j * PD);
+        pbx_apply_push_fast(c.table, row, c.table.keys[row], pm + j * PD);
       }
     }
     if (s + 1 < R) grid.sync();
@@ -518,17 +553,31 @@ static int pbx_fill_push_args(PbxPushArgs& a, const uint32_t* d_restore, int64_t
                               int dim_off, const float* d_gkeys, const int32_t* d_key2slot, int hidden, int mode,
                               float grad_scale) {
   a.restore = d_restore; a.n = n; a.dout = d_dout; a.cvm = d_cvm; a.lod = d_lod;
-  a.B = B; a.S = S; a.Eo = Eo; a.cvm_offset = cvm_offset; a.dim_off = dim_off;
+  a.B = B; a.S = S; a.Eo = Eo; a.cvm_offset = cvm_offset; a.dim_off = dim_off; a.ld_dout = S * Eo;
   a.gkeys = d_gkeys; a.key2slot = d_key2slot; a.hidden = hidden; a.mode = mode; a.grad_scale = grad_scale;
   return 0;
 }
 
 // mode 0: d_dout [B, S*Eo] pooled-output grads, d_cvm [B, cvm_offset], d_lod [S*B+1]
 // mode 1: d_gkeys [n, hidden] per-occurrence grads, d_key2slot [n]
+int pbx_sparse_push_ex(void* hnd, const uint32_t* d_restore, int64_t n, const float* d_dout, int ld_dout,
+                       const float* d_cvm, const int32_t* d_lod, int B, int S, int Eo, int cvm_offset, int dim_off,
+                       const float* d_gkeys, const int32_t* d_key2slot, int hidden, int mode, float grad_scale,
+                       cudaStream_t st);
 int pbx_sparse_push(void* hnd, const uint32_t* d_restore, int64_t n, const float* d_dout, const float* d_cvm,
                     const int32_t* d_lod, int B, int S, int Eo, int cvm_offset, int dim_off, const float* d_gkeys,
                     const int32_t* d_key2slot, int hidden, int mode, float grad_scale, cudaStream_t st) {
+  return pbx_sparse_push_ex(hnd, d_restore, n, d_dout, S * Eo, d_cvm, d_lod, B, S, Eo, cvm_offset, dim_off, d_gkeys,
+                            d_key2slot, hidden, mode, grad_scale, st);
+}
+// ld_dout: words between rows of d_dout (lets the pooled gradient live inside a wider tensor,
+// e.g. the gradient of the concatenated tower input)
+int pbx_sparse_push_ex(void* hnd, const uint32_t* d_restore, int64_t n, const float* d_dout, int ld_dout,
+                       const float* d_cvm, const int32_t* d_lod, int B, int S, int Eo, int cvm_offset, int dim_off,
+                       const float* d_gkeys, const int32_t* d_key2slot, int hidden, int mode, float grad_scale,
+                       cudaStream_t st) {
   PbxSparseCtx* c = (PbxSparseCtx*)hnd;
+  if (mode == 0) PBX_REQUIRE(ld_dout >= S * Eo, "ld_dout %d < S*Eo %d", ld_dout, S * Eo);
   PBX_REQUIRE(c->h.table.L.embedx_dim <= 256, "embedx_dim > 256 not supported by the push kernel");
   if (mode == 0)
     PBX_REQUIRE(Eo + dim_off == 3 + c->h.table.L.embedx_dim, "pooled width %d + %d != hidden %d", Eo, dim_off,
@@ -541,6 +590,7 @@ int pbx_sparse_push(void* hnd, const uint32_t* d_restore, int64_t n, const float
   memset(&args, 0, sizeof(args));
   pbx_fill_push_args(args.a[0], d_restore, n, d_dout, d_cvm, d_lod, B, S, Eo, cvm_offset, dim_off, d_gkeys,
                      d_key2slot, hidden, mode, grad_scale);
+  if (mode == 0) args.a[0].ld_dout = ld_dout;
   const PbxSparseDev* dctx = c->d;
   int nvr = 1;
   void* kargs[] = {(void*)&dctx, (void*)&nvr, (void*)&args};

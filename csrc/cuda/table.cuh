@@ -166,6 +166,80 @@ __device__ __forceinline__ void pbx_apply_push(const PbxTableView& t, uint32_t s
   if (t.dirty) t.dirty[slot_idx] = 1;
 }
 
+// Register-resident Adagrad update for a compile-time embedx width: the whole row (stride
+// = ceil4(9 + D) words) and the push record are moved with 16-byte loads/stores and the math
+// runs on registers.  Same arithmetic and order as pbx_apply_push (Adagrad branch).
+template <int D>
+__device__ __forceinline__ void pbx_apply_push_adagrad_vec(const PbxTableView& t, uint32_t slot_idx, uint64_t key,
+                                                           const float* __restrict__ push) {
+  constexpr int S4 = (9 + D + 3) / 4;
+  constexpr int P4 = (4 + D + 3) / 4;
+  constexpr int OFF_MF = 3 + D, OFF_T = 4 + D, OFF_ES = 7 + D, OFF_XS = 8 + D;
+  float p[P4 * 4];
+#pragma unroll
+  for (int i = 0; i < P4; ++i) {
+    float4 v = __ldcg(reinterpret_cast<const float4*>(push) + i);
+    p[4 * i] = v.x; p[4 * i + 1] = v.y; p[4 * i + 2] = v.z; p[4 * i + 3] = v.w;
+  }
+  const float g_show = p[1], g_click = p[2];
+  if (g_show <= 0.f) return;
+  float4* rowv = reinterpret_cast<float4*>(t.vals + (uint64_t)slot_idx * (S4 * 4));
+  float r[S4 * 4];
+#pragma unroll
+  for (int i = 0; i < S4; ++i) {
+    float4 v = rowv[i];
+    r[4 * i] = v.x; r[4 * i + 1] = v.y; r[4 * i + 2] = v.z; r[4 * i + 3] = v.w;
+  }
+  const PbxSparseOptConfig& c = t.cfg;
+  r[OFF_T + 1] = p[0];
+  const float show = r[0] + g_show, click = r[1] + g_click;
+  r[0] = show;
+  r[1] = click;
+  r[OFF_T + 0] += c.nonclk_coeff * (g_show - g_click) + c.clk_coeff * g_click;
+  r[OFF_T + 2] = 0.f;
+  const float inv = 1.f / g_show;
+  {  // embed_w
+    float ratio = c.learning_rate * sqrtf(c.initial_g2sum / (c.initial_g2sum + r[OFF_ES]));
+    float sg = p[3] * inv;
+    r[2] = fminf(fmaxf(r[2] + sg * ratio, c.min_bound), c.max_bound);
+    r[OFF_ES] += sg * sg;
+  }
+  if (r[OFF_MF] == 0.f) {
+    if (c.mf_create_thresholds <= c.nonclk_coeff * (show - click) + c.clk_coeff * click) {
+      r[OFF_MF] = (float)D;
+#pragma unroll
+      for (int i = 0; i < D; ++i) r[3 + i] = pbx_uniform01(key, (uint32_t)i, t.seed) * c.mf_initial_range;
+    }
+  } else {
+    float ratio = c.mf_learning_rate * sqrtf(c.mf_initial_g2sum / (c.mf_initial_g2sum + r[OFF_XS]));
+    float add = 0.f;
+#pragma unroll
+    for (int i = 0; i < D; ++i) {
+      float sg = p[4 + i] * inv;
+      r[3 + i] = fminf(fmaxf(r[3 + i] + sg * ratio, c.mf_min_bound), c.mf_max_bound);
+      add += sg * sg;
+    }
+    r[OFF_XS] += add / (float)D;
+  }
+#pragma unroll
+  for (int i = 0; i < S4; ++i) rowv[i] = make_float4(r[4 * i], r[4 * i + 1], r[4 * i + 2], r[4 * i + 3]);
+  if (t.dirty) t.dirty[slot_idx] = 1;
+}
+
+// dispatch: vectorised Adagrad for the common widths, generic scalar path otherwise
+__device__ __forceinline__ void pbx_apply_push_fast(const PbxTableView& t, uint32_t slot_idx, uint64_t key,
+                                                    const float* push) {
+  if (t.L.optimizer == PBX_OPT_ADAGRAD) {
+    switch (t.L.embedx_dim) {
+      case 8: pbx_apply_push_adagrad_vec<8>(t, slot_idx, key, push); return;
+      case 16: pbx_apply_push_adagrad_vec<16>(t, slot_idx, key, push); return;
+      case 32: pbx_apply_push_adagrad_vec<32>(t, slot_idx, key, push); return;
+      default: break;   // wider rows would spill under the 128-register budget of 512-thread CTAs
+    }
+  }
+  pbx_apply_push(t, slot_idx, key, push);
+}
+
 // Host-side table object (opaque to callers; see include/pbx_cuda.h)
 struct PbxTable {
   PbxTableView view;

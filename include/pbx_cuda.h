@@ -62,6 +62,11 @@ int pbx_sparse_pull_ex(void* ctx, const uint64_t* d_keys, int64_t n, const int32
 int pbx_sparse_push(void* ctx, const uint32_t* d_restore, int64_t n, const float* d_dout, const float* d_cvm,
                     const int32_t* d_lod, int B, int S, int Eo, int cvm_offset, int dim_off, const float* d_gkeys,
                     const int32_t* d_key2slot, int hidden, int mode, float grad_scale, pbx_stream_t stream);
+/* as pbx_sparse_push, with an explicit row stride (in words) of d_dout */
+int pbx_sparse_push_ex(void* ctx, const uint32_t* d_restore, int64_t n, const float* d_dout, int ld_dout,
+                       const float* d_cvm, const int32_t* d_lod, int B, int S, int Eo, int cvm_offset, int dim_off,
+                       const float* d_gkeys, const int32_t* d_key2slot, int hidden, int mode, float grad_scale,
+                       pbx_stream_t stream);
 int pbx_sparse_pull_emu(void* const* ctxs, int nranks, const uint64_t* const* d_keys, const int64_t* n,
                         uint32_t* const* d_restore, pbx_stream_t stream);
 int pbx_sparse_push_emu(void* const* ctxs, int nranks, const uint32_t* const* d_restore, const int64_t* n,

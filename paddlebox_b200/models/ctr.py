@@ -44,15 +44,17 @@ class CTRModelBase(nn.Module):
         feats = d[:, self.n_labels:self.n_labels + self.dense_dim]
         return labels, feats
 
-    def sparse_features(self, batch: SlotBatch, click: torch.Tensor) -> torch.Tensor:
-        """[B, S*Eo] pooled slot embeddings; ``click`` [B] becomes the clk column of the push."""
+    def sparse_features(self, batch: SlotBatch, click: torch.Tensor, dense: torch.Tensor | None = None):
+        """[B, S*Eo (+ Dd)] pooled slot embeddings (and dense features appended in the same
+        buffer); ``click`` [B] becomes the clk column of the push."""
         cvm = torch.stack([torch.ones_like(click), click], 1)
-        return sparse_embedding_pool(batch, cvm, BoxWrapper.get_instance(), self.attrs)
+        return sparse_embedding_pool(batch, cvm, BoxWrapper.get_instance(), self.attrs, dense=dense)
 
     def features(self, batch: SlotBatch):
+        """(x, pooled, labels): x [B, input_width] tower input, pooled = its sparse columns (a view)."""
         labels, feats = self.split_dense(batch)
-        pooled = self.sparse_features(batch, labels[:, 0].contiguous())
-        x = torch.cat([pooled, feats], 1) if self.dense_dim else pooled
+        x = self.sparse_features(batch, labels[:, 0].contiguous(), feats if self.dense_dim else None)
+        pooled = x[:, :self.sparse_width]
         if self.data_norm is not None:
             x = self.data_norm(x)
         return x, pooled, labels
@@ -105,7 +107,7 @@ class WideDeep(CTRModelBase):
     def forward(self, batch: SlotBatch):
         x, pooled, labels = self.features(batch)
         E = self.attrs.out_width(self.slot_width)
-        wide = pooled.view(-1, self.num_slots, E)[:, :, 2].sum(1)      # sum of embed_w
+        wide = pooled[:, 2::E].sum(1)                                   # sum of embed_w over slots
         if self.dense_dim:
             wide = wide + x[:, self.sparse_width:] @ self.wide_dense
         logit = self.tower(x).view(-1) + wide + self.wide_bias
@@ -124,7 +126,8 @@ class DeepFM(CTRModelBase):
     def forward(self, batch: SlotBatch):
         x, pooled, labels = self.features(batch)
         E = self.attrs.out_width(self.slot_width)
-        fm = F.fm_interaction(pooled, self.num_slots, E, 2, 3, self.embedx_dim)
+        fm_in = x if self.data_norm is None else pooled     # x's leading columns are the pooled slots
+        fm = F.fm_interaction(fm_in, self.num_slots, E, 2, 3, self.embedx_dim)
         logit = self.tower(x).view(-1) + fm + self.bias
         loss, pred = F.sigmoid_log_loss(logit, labels[:, 0])
         return loss, {"pred": pred, "label": labels[:, 0]}

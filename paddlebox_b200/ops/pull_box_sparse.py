@@ -145,11 +145,20 @@ def pull_box_extended_sparse(batch: SlotBatch, size: int, extend_size: int, box:
 
 class _SparseEmbeddingPool(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, anchor, box, batch, cvm, attrs):
+    def forward(ctx, anchor, box, batch, cvm, attrs, dense):
         B, S = batch.batch_size, batch.num_slots
         vals, restore = box.pull_sparse(batch.keys, batch.n_dev)
-        out = seqpool_cvm_forward(vals, batch.lod, B, S, attrs, box.hidden, restore=restore)
-        ctx.box, ctx.batch, ctx.attrs, ctx.restore = box, batch, attrs, restore
+        sw = S * attrs.out_width(box.hidden)
+        if dense is not None and vals.is_cuda:
+            # pooled embeddings and dense features land in ONE row-major buffer: no concat pass
+            out = torch.empty(B, sw + dense.shape[1], dtype=torch.float32, device=vals.device)
+            seqpool_cvm_forward(vals, batch.lod, B, S, attrs, box.hidden, restore=restore, out=out)
+            out[:, sw:] = dense
+        else:
+            out = seqpool_cvm_forward(vals, batch.lod, B, S, attrs, box.hidden, restore=restore)
+            if dense is not None:
+                out = torch.cat([out, dense], 1)
+        ctx.box, ctx.batch, ctx.attrs, ctx.restore, ctx.sw = box, batch, attrs, restore, sw
         ctx.save_for_backward(cvm)
         return out
 
@@ -158,26 +167,34 @@ class _SparseEmbeddingPool(torch.autograd.Function):
         box, batch, attrs = ctx.box, ctx.batch, ctx.attrs
         (cvm,) = ctx.saved_tensors
         B, S = batch.batch_size, batch.num_slots
+        nothing = (torch.zeros_like(_anchor(dout.device)), None, None, None, None, None)
         if box._test_mode:
-            return torch.zeros_like(_anchor(dout.device)), None, None, None, None
+            return nothing
         fused_ok = (dout.is_cuda and attrs.cvm_offset == 2 and attrs.embedx_concate_size == 1
                     and attrs.variant == 0)
         if fused_ok:
             Eo = attrs.out_width(box.hidden)
-            box.engine.push_pooled(ctx.restore, dout.contiguous(), cvm.contiguous(), batch.lod, B, S, Eo, 2,
-                                   attrs.dim_off(), -float(B))
+            if dout.stride(1) != 1:
+                dout = dout.contiguous()
+            # the pooled gradient is read in place from the (wider) input gradient: row stride = ld
+            box.engine.push_pooled(ctx.restore, dout, cvm.contiguous(), batch.lod, B, S, Eo, 2,
+                                   attrs.dim_off(), -float(B), ld_dout=dout.stride(0))
         else:
-            dx = seqpool_cvm_backward(dout.contiguous(), cvm, batch.lod, B, S, batch.N, attrs, box.hidden)
+            dsp = dout[:, :ctx.sw].contiguous()
+            dx = seqpool_cvm_backward(dsp, cvm, batch.lod, B, S, batch.N, attrs, box.hidden)
             box.push_sparse_grad(batch.keys, ctx.restore, dx, batch.key2slot(), B)
-        return torch.zeros_like(_anchor(dout.device)), None, None, None, None
+        return nothing
 
 
 def sparse_embedding_pool(batch: SlotBatch, cvm: torch.Tensor, box: BoxWrapper | None = None,
-                          attrs: SeqpoolAttrs | None = None, **kw) -> torch.Tensor:
+                          attrs: SeqpoolAttrs | None = None, dense: torch.Tensor | None = None,
+                          **kw) -> torch.Tensor:
     """pull_box_sparse + fused_seqpool_cvm in one differentiable op -> [B, S*Eo].
 
     ``cvm`` [B, 2] holds (show = 1, clk = label) per instance; in backward it becomes the
-    show/click count columns of the push."""
+    show/click count columns of the push.  With ``dense`` [B, Dd] the result is
+    ``[B, S*Eo + Dd]`` — the tower input — written in one buffer (no concat); ``dense`` gets no
+    gradient (it is input data)."""
     box = box or BoxWrapper.get_instance()
     attrs = attrs or SeqpoolAttrs(**kw)
-    return _SparseEmbeddingPool.apply(_anchor(batch.keys.device), box, batch, cvm, attrs)
+    return _SparseEmbeddingPool.apply(_anchor(batch.keys.device), box, batch, cvm, attrs, dense)

@@ -95,13 +95,17 @@ class SparseEngine:
         return restore[:n]
 
     def push_pooled(self, restore: torch.Tensor, dout: torch.Tensor, cvm: torch.Tensor, lod: torch.Tensor, B: int,
-                    S: int, Eo: int, cvm_offset: int, dim_off: int, grad_scale: float) -> None:
+                    S: int, Eo: int, cvm_offset: int, dim_off: int, grad_scale: float,
+                    ld_dout: int | None = None) -> None:
         """Fused seqpool/CVM backward + merge-by-key + all-to-all + optimizer update.
-        ``dout`` [B, S*Eo] contiguous, ``cvm`` [B, cvm_offset], ``lod`` int32 [S*B+1]."""
-        assert dout.is_contiguous() and dout.shape == (B, S * Eo) and dout.dtype == torch.float32
-        N.check(N.cuda().pbx_sparse_push(self._h, N.ptr(restore), C.c_int64(restore.numel()), N.ptr(dout),
-                                         N.ptr(cvm), N.ptr(lod), B, S, Eo, cvm_offset, dim_off, None, None, 0, 0,
-                                         C.c_float(grad_scale), N.stream_ptr()), "pbx_sparse_push")
+        ``dout`` [B, >= S*Eo] with unit column stride (row stride ``ld_dout``, default the tensor's),
+        ``cvm`` [B, cvm_offset], ``lod`` int32 [S*B+1]."""
+        ld = dout.stride(0) if ld_dout is None else ld_dout
+        assert dout.stride(1) == 1 and dout.shape[0] == B and dout.shape[1] >= S * Eo and ld >= S * Eo \
+            and dout.dtype == torch.float32
+        N.check(N.cuda().pbx_sparse_push_ex(self._h, N.ptr(restore), C.c_int64(restore.numel()), N.ptr(dout), ld,
+                                            N.ptr(cvm), N.ptr(lod), B, S, Eo, cvm_offset, dim_off, None, None, 0,
+                                            0, C.c_float(grad_scale), N.stream_ptr()), "pbx_sparse_push")
 
     def push_keys(self, restore: torch.Tensor, grads: torch.Tensor, key2slot: torch.Tensor, cvm_offset: int,
                   grad_scale: float) -> None:
