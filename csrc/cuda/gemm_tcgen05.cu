@@ -36,6 +36,8 @@ struct GemmEpilogue {
   int relu;
   int accumulate;             // atomicAdd into out_f32 (split-K)
   float alpha;
+  float* col_out;             // optional: output column `col_split` goes to col_out[row] instead of
+  int col_split;              // out_f32 (bias gradient from a ones row appended to the B operand)
 };
 
 // ---------------- PTX wrappers ----------------
@@ -132,6 +134,8 @@ struct SmemLayout {
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int TOTAL = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  // the epilogue reuses the stage memory for a row-major and a transposed bf16 staging tile
+  static_assert(BM * (BN + 8) * 2 + BN * (BM + 8) * 2 <= STAGES * STAGE_BYTES, "staging tiles do not fit");
 };
 
 template <int BN>
@@ -212,8 +216,18 @@ k_gemm_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       __syncwarp();
     } else {
       // ===== epilogue: warps 2..5, TMEM lane quadrant = warp % 4 =====
+      // bf16 outputs are staged through shared memory (the pipeline stages are free once the
+      // accumulator is complete) so that both the row-major tile and its transpose leave the SM
+      // as 16-byte, fully coalesced stores.  (Writing the transpose straight from registers
+      // costs one 2-byte store instruction per element: ncu showed the epilogue at ~10x the
+      // tensor-pipe time.)
       const int q = warp & 3;
-      const int row = m0 + q * 32 + lane;
+      const int rl = q * 32 + lane;          // row inside the tile
+      const int row = m0 + rl;
+      constexpr int LDC = BN + 8, LDT = BM + 8;
+      __nv_bfloat16* sC = reinterpret_cast<__nv_bfloat16*>(smem);
+      __nv_bfloat16* sT = sC + BM * LDC;
+      const bool stage = ep.out_bf16 != nullptr || ep.out_t != nullptr;
       mbar_wait(tmem_full_bar, 0);
       tc_fence_after();
 #pragma unroll 1
@@ -232,51 +246,104 @@ k_gemm_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         }
         if (ep.mask && row < M) {
           const __nv_bfloat16* mrow = ep.mask + (int64_t)row * ep.ld_mask + n0 + c0;
+          if (n0 + c0 + 32 <= N && (ep.ld_mask & 7) == 0) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j)
-            if (n0 + c0 + j < N && !(__bfloat162float(mrow[j]) > 0.f)) v[j] = 0.f;
-        }
-        if (row < M) {
-          if (ep.out_bf16) {
-            __nv_bfloat16* o = ep.out_bf16 + (int64_t)row * ep.ld_out + n0 + c0;
-            if (n0 + c0 + 32 <= N && (ep.ld_out & 7) == 0) {
+            for (int j = 0; j < 32; j += 8) {
+              const uint4 mk = __ldg(reinterpret_cast<const uint4*>(mrow + j));
+              const __nv_bfloat16* mb = reinterpret_cast<const __nv_bfloat16*>(&mk);
 #pragma unroll
-              for (int j = 0; j < 32; j += 8) {
-                __nv_bfloat162 p0 = __floats2bfloat162_rn(v[j], v[j + 1]);
-                __nv_bfloat162 p1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
-                __nv_bfloat162 p2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]);
-                __nv_bfloat162 p3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
-                uint4 pk;
-                pk.x = *reinterpret_cast<uint32_t*>(&p0);
-                pk.y = *reinterpret_cast<uint32_t*>(&p1);
-                pk.z = *reinterpret_cast<uint32_t*>(&p2);
-                pk.w = *reinterpret_cast<uint32_t*>(&p3);
-                *reinterpret_cast<uint4*>(o + j) = pk;
-              }
-            } else {
-              for (int j = 0; j < 32; ++j)
-                if (n0 + c0 + j < N) o[j] = __float2bfloat16(v[j]);
+              for (int e = 0; e < 8; ++e)
+                if (!(__bfloat162float(mb[e]) > 0.f)) v[j + e] = 0.f;
             }
+          } else {
+            for (int j = 0; j < 32; ++j)
+              if (n0 + c0 + j < N && !(__bfloat162float(mrow[j]) > 0.f)) v[j] = 0.f;
           }
-          if (ep.out_f32) {
-            float* o = ep.out_f32 + (int64_t)row * ep.ld_f32 + n0 + c0;
-            if (ep.accumulate) {
-              for (int j = 0; j < 32; ++j)
-                if (n0 + c0 + j < N) atomicAdd(o + j, v[j]);
-            } else if (n0 + c0 + 32 <= N && (ep.ld_f32 & 3) == 0) {
+        }
+        if (stage) {
+          if (ep.out_bf16) {
 #pragma unroll
-              for (int j = 0; j < 32; j += 4)
-                *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-            } else {
-              for (int j = 0; j < 32; ++j)
-                if (n0 + c0 + j < N) o[j] = v[j];
+            for (int j = 0; j < 32; j += 8) {
+              __nv_bfloat162 p0 = __floats2bfloat162_rn(v[j], v[j + 1]);
+              __nv_bfloat162 p1 = __floats2bfloat162_rn(v[j + 2], v[j + 3]);
+              __nv_bfloat162 p2 = __floats2bfloat162_rn(v[j + 4], v[j + 5]);
+              __nv_bfloat162 p3 = __floats2bfloat162_rn(v[j + 6], v[j + 7]);
+              uint4 pk;
+              pk.x = *reinterpret_cast<uint32_t*>(&p0);
+              pk.y = *reinterpret_cast<uint32_t*>(&p1);
+              pk.z = *reinterpret_cast<uint32_t*>(&p2);
+              pk.w = *reinterpret_cast<uint32_t*>(&p3);
+              *reinterpret_cast<uint4*>(sC + rl * LDC + c0 + j) = pk;
             }
           }
           if (ep.out_t) {
-            // lanes are consecutive rows -> consecutive addresses in the transposed copy
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (n0 + c0 + j < N) ep.out_t[(int64_t)(n0 + c0 + j) * ep.ld_t + row] = __float2bfloat16(v[j]);
+            for (int j = 0; j < 32; ++j) sT[(c0 + j) * LDT + rl] = __float2bfloat16(v[j]);
+          }
+        }
+        if (ep.out_f32 && row < M) {
+          float* o = ep.out_f32 + (int64_t)row * ep.ld_f32 + n0 + c0;
+          const bool full = n0 + c0 + 32 <= N && (ep.ld_f32 & 3) == 0 &&
+                            !(ep.col_out && ep.col_split >= n0 + c0 && ep.col_split < n0 + c0 + 32);
+          if (ep.accumulate) {
+            if (full) {
+#pragma unroll
+              for (int j = 0; j < 32; j += 4) pbx_red_add_v4(o + j, v[j], v[j + 1], v[j + 2], v[j + 3]);
+            } else {
+              for (int j = 0; j < 32; ++j) {
+                const int n = n0 + c0 + j;
+                if (n >= N) break;
+                if (ep.col_out && n == ep.col_split) atomicAdd(ep.col_out + row, v[j]);
+                else atomicAdd(o + j, v[j]);
+              }
+            }
+          } else if (full) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4)
+              *reinterpret_cast<float4*>(o + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+          } else {
+            for (int j = 0; j < 32; ++j) {
+              const int n = n0 + c0 + j;
+              if (n >= N) break;
+              if (ep.col_out && n == ep.col_split) ep.col_out[row] = v[j];
+              else o[j] = v[j];
+            }
+          }
+        }
+      }
+      if (stage) {
+        asm volatile("bar.sync 1, 128;" ::: "memory");   // the four epilogue warps only
+        const int et = threadIdx.x - 64;
+        if (ep.out_bf16) {
+          constexpr int VPR = BN / 8;
+          for (int idx = et; idx < BM * VPR; idx += 128) {
+            const int r_ = idx / VPR, cv = idx % VPR;
+            const int gr = m0 + r_, gc = n0 + cv * 8;
+            if (gr >= M || gc >= N) continue;
+            const uint4 val = *reinterpret_cast<const uint4*>(sC + r_ * LDC + cv * 8);
+            __nv_bfloat16* o = ep.out_bf16 + (int64_t)gr * ep.ld_out + gc;
+            if (gc + 8 <= N && (ep.ld_out & 7) == 0) {
+              *reinterpret_cast<uint4*>(o) = val;
+            } else {
+              const __nv_bfloat16* e8 = reinterpret_cast<const __nv_bfloat16*>(&val);
+              for (int e = 0; e < 8 && gc + e < N; ++e) o[e] = e8[e];
+            }
+          }
+        }
+        if (ep.out_t) {
+          constexpr int VPR = BM / 8;
+          for (int idx = et; idx < BN * VPR; idx += 128) {
+            const int n_ = idx / VPR, mv = idx % VPR;
+            const int gn = n0 + n_, gm = m0 + mv * 8;
+            if (gn >= N || gm >= M) continue;
+            const uint4 val = *reinterpret_cast<const uint4*>(sT + n_ * LDT + mv * 8);
+            __nv_bfloat16* o = ep.out_t + (int64_t)gn * ep.ld_t + gm;
+            if (gm + 8 <= M && (ep.ld_t & 7) == 0) {
+              *reinterpret_cast<uint4*>(o) = val;
+            } else {
+              const __nv_bfloat16* e8 = reinterpret_cast<const __nv_bfloat16*>(&val);
+              for (int e = 0; e < 8 && gm + e < M; ++e) o[e] = e8[e];
+            }
           }
         }
       }
@@ -311,8 +378,9 @@ __global__ void k_gemm_simt(const __nv_bfloat16* __restrict__ A, int lda, const 
   if (ep.out_bf16) ep.out_bf16[(int64_t)row * ep.ld_out + col] = __float2bfloat16(x);
   if (ep.out_t) ep.out_t[(int64_t)col * ep.ld_t + row] = __float2bfloat16(x);
   if (ep.out_f32) {
-    if (ep.accumulate) atomicAdd(ep.out_f32 + (int64_t)row * ep.ld_f32 + col, x);
-    else ep.out_f32[(int64_t)row * ep.ld_f32 + col] = x;
+    float* dst = (ep.col_out && col == ep.col_split) ? ep.col_out + row : ep.out_f32 + (int64_t)row * ep.ld_f32 + col;
+    if (ep.accumulate) atomicAdd(dst, x);
+    else *dst = x;
   }
 }
 
@@ -377,7 +445,7 @@ extern "C" {
 int pbx_gemm_bf16_tn(const void* A, int lda, const void* B, int ldb, int M, int N, int K, const float* bias,
                      const void* mask, int ld_mask, void* out_bf16, int ld_out, void* out_t, int ld_t,
                      float* out_f32, int ld_f32, int relu, int accumulate, float alpha, int splitk, int block_n,
-                     int impl, cudaStream_t st) {
+                     int impl, float* col_out, int col_split, cudaStream_t st) {
   if (M <= 0 || N <= 0) return 0;
   PBX_REQUIRE(K > 0, "gemm: K must be positive");
   GemmEpilogue ep;
@@ -390,6 +458,8 @@ int pbx_gemm_bf16_tn(const void* A, int lda, const void* B, int ldb, int M, int 
   ep.relu = relu;
   ep.accumulate = accumulate;
   ep.alpha = alpha;
+  ep.col_out = col_out;
+  ep.col_split = col_split;
   if (splitk > 1) PBX_REQUIRE(accumulate && out_f32 && !out_bf16 && !out_t && !relu && !bias && !mask,
                               "gemm: split-K needs a pure fp32 accumulate epilogue");
   if (impl == 1) {

@@ -40,8 +40,7 @@ namespace {
 template <bool EMU>
 __device__ __forceinline__ void symm_barrier(cg::grid_group& grid, const PbxSymmDev& c, uint64_t target,
                                              bool leader_block) {
-  __threadfence_system();
-  grid.sync();
+  grid.sync();   // gpu-scope ordering of all threads' stores; the leader's fence below is system scope
   if (!EMU && c.nranks > 1) {
     if (leader_block && threadIdx.x < c.nranks) {
       int p = threadIdx.x;

@@ -91,7 +91,9 @@ int pbx_key2slot(const int32_t* d_lod, int B, int S, int64_t n, int32_t* d_out, 
 int pbx_gemm_bf16_tn(const void* A, int lda, const void* B, int ldb, int M, int N, int K, const float* bias,
                      const void* mask, int ld_mask, void* out_bf16, int ld_out, void* out_t, int ld_t,
                      float* out_f32, int ld_f32, int relu, int accumulate, float alpha, int splitk, int block_n,
-                     int impl, pbx_stream_t stream);
+                     int impl, float* col_out, int col_split, pbx_stream_t stream);
+/* col_out/col_split (optional): output column `col_split` is written to col_out[row] instead of
+ * out_f32 — with a row of ones appended to B this yields the bias gradient inside the wgrad GEMM. */
 
 /* ---- dense helpers (csrc/cuda/dense_ops.cu) --------------------------------- */
 int pbx_cast_transpose(const float* x, int ld, int M, int K, void* out_bf16, int ldo, void* out_t, int ldt,

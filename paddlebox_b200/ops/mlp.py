@@ -35,8 +35,10 @@ def gemm_impl() -> int:
 
 def gemm_bf16_tn(A: torch.Tensor, B: torch.Tensor, M: int, Nn: int, K: int, *, bias=None, mask=None, out_bf16=None,
                  out_t=None, out_f32=None, relu=False, accumulate=False, alpha=1.0, splitk=1, block_n=0,
-                 impl=None) -> None:
-    """A: bf16 [>=M, lda], B: bf16 [>=N, ldb] (row strides taken from the tensors)."""
+                 impl=None, col_out=None, col_split: int = -1) -> None:
+    """A: bf16 [>=M, lda], B: bf16 [>=N, ldb] (row strides taken from the tensors).
+    ``col_out`` / ``col_split``: output column ``col_split`` goes to ``col_out[row]`` instead of
+    ``out_f32`` (bias gradient when B carries a row of ones)."""
     assert A.dtype == torch.bfloat16 and B.dtype == torch.bfloat16 and A.is_cuda
     N.check(N.cuda().pbx_gemm_bf16_tn(
         N.ptr(A), A.stride(0), N.ptr(B), B.stride(0), M, Nn, K, N.ptr(bias),
@@ -45,7 +47,7 @@ def gemm_bf16_tn(A: torch.Tensor, B: torch.Tensor, M: int, Nn: int, K: int, *, b
         N.ptr(out_t), out_t.stride(0) if out_t is not None else 0,
         N.ptr(out_f32), out_f32.stride(0) if out_f32 is not None else 0,
         int(relu), int(accumulate), C.c_float(alpha), splitk, block_n,
-        gemm_impl() if impl is None else impl, N.stream_ptr()), "pbx_gemm_bf16_tn")
+        gemm_impl() if impl is None else impl, N.ptr(col_out), col_split, N.stream_ptr()), "pbx_gemm_bf16_tn")
 
 
 def cast_transpose(x: torch.Tensor, out: torch.Tensor | None, out_t: torch.Tensor | None) -> None:
@@ -70,7 +72,10 @@ class _Workspace:
         self.B = B
         # H[l]: [B, dims[l]] activations (l = 0 is the cast input), Ht[l] their transposes
         self.H = [torch.zeros(B, _pad8(d), dtype=bf, device=device) for d in dims[:-1]]
-        self.Ht = [torch.zeros(d, Bp, dtype=bf, device=device) for d in dims[:-1]]
+        # one extra row of ones: the wgrad GEMM then emits the bias gradient as column d
+        self.Ht = [torch.zeros(d + 1, Bp, dtype=bf, device=device) for d in dims[:-1]]
+        for t in self.Ht:
+            t[-1, :B] = 1.0
         # dZ[l]: grad w.r.t. pre-activation of layer l (1-based), and transposes
         self.dZ = [torch.zeros(B, _pad8(d), dtype=bf, device=device) for d in dims[1:]]
         self.dZt = [torch.zeros(d, Bp, dtype=bf, device=device) for d in dims[1:]]
@@ -193,8 +198,9 @@ class FusedMLP(nn.Module):
                 b.grad = torch.zeros_like(b.data)
             # wgrad: dW[N, K] += dZ^T[N, B] . (H^T[K, B])^T   (split-K over the batch)
             splitk = max(1, min(16, B // 512))
-            gemm_bf16_tn(ws.dZt[l], ws.Ht[l], Nn, K, B, out_f32=w.grad, accumulate=True, splitk=splitk)
-            colsum_bf16(ws.dZ[l], B, Nn, b.grad)
+            # (the ones row of Ht makes output column K the bias gradient: no separate column-sum pass)
+            gemm_bf16_tn(ws.dZt[l], ws.Ht[l], Nn, K + 1, B, out_f32=w.grad, accumulate=True, splitk=splitk,
+                         col_out=b.grad, col_split=K)
             if l > 0:
                 # dgrad fused with the ReLU mask of the previous activation
                 gemm_bf16_tn(ws.dZ[l], self._wbt[l], B, K, Nn, mask=ws.H[l], out_bf16=ws.dZ[l - 1],

@@ -1,0 +1,105 @@
+"""``BoxPSOptimizer`` and the collective "transpiler" of the reference, re-expressed.
+
+Reference: ``fluid.optimizer.BoxPSOptimizer`` (python/paddle/fluid/optimizer.py:7315-7611)
+wraps a dense optimizer, optionally splits the program by ``cut_list`` and stamps
+``program._pipeline_opt = {trainer: BoxPSTrainer, device_worker: BoxPSWorker,
+param_need_sync: [...]}``; the collective transpiler
+(python/paddle/fluid/transpiler/collective.py:421-740) rewrites the program with
+``c_comm_init_all`` + per-grad / fused ``c_allreduce_sum`` ops.  With PyTorch autograd there
+is no program to rewrite: ``minimize`` attaches a ``TrainerConfig`` to the model, and the
+data-parallel collectives are chosen by ``sync_dense_mode``.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+
+import torch
+
+from .trainer import CTRTrainer, TrainerConfig
+
+
+@dataclass
+class DenseOptimizerSpec:
+    kind: str = "adam"
+    lr: float = 1e-3
+    beta1: float = 0.9
+    beta2: float = 0.999
+    epsilon: float = 1e-8
+    weight_decay: float = 0.0
+
+
+def Adam(learning_rate=1e-3, beta1=0.9, beta2=0.999, epsilon=1e-8, **_):
+    return DenseOptimizerSpec("adam", learning_rate, beta1, beta2, epsilon)
+
+
+def SGD(learning_rate=1e-2, **_):
+    return DenseOptimizerSpec("sgd", learning_rate)
+
+
+class BoxPSOptimizer:
+    """``BoxPSOptimizer(Adam(...), cut_list=[], place_list=[...], concurrency_list=[...],
+    queue_size=30, sync_steps=1, start_cpu_core_id=0)``."""
+
+    def __init__(self, optimizer: DenseOptimizerSpec, cut_list=None, place_list=None, concurrency_list=None,
+                 queue_size: int = 30, sync_steps: int = 1, start_cpu_core_id: int = 0, sync_dense_mode: str | int =
+                 "allreduce", async_mode: bool = False, sync_one_ring: bool = False, dump_thread_num: int = 1):
+        self._optimizer = optimizer
+        self._cut_list = cut_list or []
+        self._place_list = place_list or []
+        self._concurrency_list = concurrency_list or []
+        self._queue_size = queue_size
+        self._sync_steps = sync_steps
+        self._start_cpu_core_id = start_cpu_core_id
+        # reference enum: DenseKStepNode=1, DenseKStepALL=2, DenseDataNormal=3 (boxps_worker.cc:393-395)
+        modes = {1: "kstep", 2: "kstep", 3: "allreduce", 0: "none"}
+        self._mode = modes.get(sync_dense_mode, sync_dense_mode)
+        self._async = async_mode
+        self._dump_thread_num = dump_thread_num
+
+    def minimize(self, model: torch.nn.Module, startup_program=None, parameter_list=None, no_grad_set=None):
+        """Attach the trainer configuration to ``model`` (the "program"); returns the config.
+        ``Executor.train_from_dataset(model, dataset)`` picks it up."""
+        if self._cut_list:
+            raise NotImplementedError("pipeline-by-section (cut_list) is not used by BoxPSWorker in the reference "
+                                      "either (SURVEY §2.7); train the whole model on every GPU")
+        cfg = TrainerConfig(dense_lr=self._optimizer.lr, dense_optimizer=self._optimizer.kind,
+                            sync_dense_mode=self._mode, sync_weight_step=max(1, self._sync_steps),
+                            async_mode=self._async, dump_thread_num=self._dump_thread_num)
+        model._pipeline_opt = cfg
+        model._param_need_sync = [n for n, p in model.named_parameters() if p.requires_grad]
+        return cfg
+
+    def build_trainer(self, model: torch.nn.Module, box=None) -> CTRTrainer:
+        cfg = getattr(model, "_pipeline_opt", None) or self.minimize(model)
+        return CTRTrainer(model, box, cfg)
+
+
+class GradAllReduce:
+    """Stand-in for ``transpiler.collective.GradAllReduce / SingleProcessMultiThread /
+    MultiThread``: there is nothing to transpile; ``transpile`` records the choice and returns
+    the sync mode a ``TrainerConfig`` should use."""
+
+    def __init__(self, nrings: int = 1, fuse_all_reduce: bool = True):
+        self.nrings, self.fuse = nrings, fuse_all_reduce
+        self.mode = "allreduce"
+
+    def transpile(self, startup_program=None, main_program=None, rank: int = 0, endpoints=None,
+                  current_endpoint=None, wait_port=None):
+        if main_program is not None and hasattr(main_program, "_pipeline_opt") and main_program._pipeline_opt:
+            main_program._pipeline_opt.sync_dense_mode = self.mode
+        return self.mode
+
+
+class LocalSGD(GradAllReduce):
+    """K-step model averaging (reference ``LocalSGD`` transpiler / ``sync_weight_step``)."""
+
+    def __init__(self, k_steps: int = 1, **kw):
+        super().__init__(**kw)
+        self.mode = "kstep"
+        self.k_steps = k_steps
+
+    def transpile(self, startup_program=None, main_program=None, **kw):
+        mode = super().transpile(startup_program, main_program, **kw)
+        if main_program is not None and getattr(main_program, "_pipeline_opt", None):
+            main_program._pipeline_opt.sync_weight_step = self.k_steps
+        return mode

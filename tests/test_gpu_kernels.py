@@ -314,6 +314,13 @@ def test_gemm_bf16_tn(impl, M, N, K):
     acc = torch.ones(M, N, device=dev())
     gemm_bf16_tn(A, Bm, M, N, K, out_f32=acc, accumulate=True, splitk=4 if impl == 0 else 1, impl=impl)
     assert torch.allclose(acc, ref + 1, **tol)
+    # bias-gradient column: the last output column is routed to a separate vector
+    if N > 1:
+        acc2 = torch.zeros(M, N - 1, device=dev())
+        colv = torch.zeros(M, device=dev())
+        gemm_bf16_tn(A, Bm, M, N, K, out_f32=acc2, accumulate=True, splitk=2 if impl == 0 else 1, impl=impl,
+                     col_out=colv, col_split=N - 1)
+        assert torch.allclose(acc2, ref[:, :N - 1], **tol) and torch.allclose(colv, ref[:, N - 1], **tol)
 
 
 def test_fused_mlp_matches_torch():
