@@ -236,13 +236,30 @@ k_gemm_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
         tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
         if (n0 + c0 >= N) continue;
         float v[32];
+        if (ep.bias && n0 + c0 + 32 <= N && ((n0 + c0) & 3) == 0 && ((uintptr_t)ep.bias & 15) == 0) {
+          // the 32 bias values of this chunk as 8 independent 16-byte (warp-uniform) loads
+          float4 bq[8];
 #pragma unroll
-        for (int j = 0; j < 32; ++j) {
-          float x = __uint_as_float(r[j]) * ep.alpha;
-          const int n = n0 + c0 + j;
-          if (ep.bias && n < N) x += __ldg(ep.bias + n);
-          if (ep.relu) x = fmaxf(x, 0.f);
-          v[j] = x;
+          for (int j = 0; j < 8; ++j) bq[j] = __ldg(reinterpret_cast<const float4*>(ep.bias + n0 + c0) + j);
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            v[4 * j] = __uint_as_float(r[4 * j]) * ep.alpha + bq[j].x;
+            v[4 * j + 1] = __uint_as_float(r[4 * j + 1]) * ep.alpha + bq[j].y;
+            v[4 * j + 2] = __uint_as_float(r[4 * j + 2]) * ep.alpha + bq[j].z;
+            v[4 * j + 3] = __uint_as_float(r[4 * j + 3]) * ep.alpha + bq[j].w;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            float x = __uint_as_float(r[j]) * ep.alpha;
+            const int n = n0 + c0 + j;
+            if (ep.bias && n < N) x += __ldg(ep.bias + n);
+            v[j] = x;
+          }
+        }
+        if (ep.relu) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
         }
         if (ep.mask && row < M) {
           const __nv_bfloat16* mrow = ep.mask + (int64_t)row * ep.ld_mask + n0 + c0;

@@ -1,0 +1,250 @@
+"""Framework-level pieces that run anywhere: flags, dense checkpoint format, metric variants,
+CTR op family oracles, side tables, file manager, BoxPSOptimizer, data generator."""
+import os
+import struct
+
+import numpy as np
+import pytest
+import torch
+
+from paddlebox_b200 import checkpoint as ckpt
+from paddlebox_b200.flags import FLAGS, get_flags, set_flags
+from paddlebox_b200.metrics import create_metric
+from paddlebox_b200.ops import ctr_ops as O
+from paddlebox_b200.ops import functional as F
+from paddlebox_b200.ops import reference as R
+from paddlebox_b200.ops.seqpool import fused_seqpool_cvm, split_slots
+from paddlebox_b200.side_tables import BoxFileMgr, GpuReplicaCache, InputTable
+
+
+def test_flags_env_and_setters(monkeypatch):
+    assert FLAGS.enable_pullpush_dedup_keys is True
+    set_flags({"FLAGS_padbox_record_pool_max_size": "123", "check_nan_inf": 1})
+    assert get_flags(["padbox_record_pool_max_size", "FLAGS_check_nan_inf"]) == {
+        "padbox_record_pool_max_size": 123, "FLAGS_check_nan_inf": True}
+    FLAGS.check_nan_inf = False
+    with pytest.raises(AttributeError):
+        FLAGS.no_such_flag = 1
+    assert "gpugraph_hbm_table_load_factor" in FLAGS.describe()
+
+
+def test_lod_tensor_format_roundtrip_and_layout(tmp_path):
+    t = torch.arange(12, dtype=torch.float32).reshape(3, 4)
+    raw = ckpt.serialize_lod_tensor(t)
+    # u32 version | u64 lod levels | u32 tensor version | i32 desc size | desc | data
+    assert struct.unpack_from("<I", raw, 0)[0] == 0 and struct.unpack_from("<Q", raw, 4)[0] == 0
+    dsize = struct.unpack_from("<i", raw, 16)[0]
+    desc = raw[20:20 + dsize]
+    assert desc == b"\x08\x05\x10\x03\x10\x04"          # data_type FP32(5), dims 3, 4
+    assert raw[20 + dsize:] == t.numpy().tobytes()
+    back, lod = ckpt.deserialize_lod_tensor(raw)
+    assert torch.equal(back, t) and lod == []
+    b16 = torch.randn(5, 2).to(torch.bfloat16)
+    assert torch.equal(ckpt.deserialize_lod_tensor(ckpt.serialize_lod_tensor(b16))[0], b16)
+    from paddlebox_b200.models.ctr import CtrDnn
+    from paddlebox_b200.parallel.dense import DenseParamStore
+    m = CtrDnn(num_slots=2, embedx_dim=4, dense_dim=1, hidden=(8,))
+    store = DenseParamStore(m)
+    store.m.normal_()
+    names = ckpt.save_persistables(m, str(tmp_path / "dense"), store)
+    assert "fc_0.w_0" in names and "fc_0.b_0" in names and "fc_0.w_0_moment1_0" in names
+    m2 = CtrDnn(num_slots=2, embedx_dim=4, dense_dim=1, hidden=(8,))
+    store2 = DenseParamStore(m2)
+    ckpt.load_persistables(m2, str(tmp_path / "dense"), store2)
+    for (n1, p1), (n2, p2) in zip(m.named_dense_params(), m2.named_dense_params()):
+        assert n1 == n2 and torch.equal(p1, p2)
+    for p, off in zip(store.params, store.offsets):      # (padding words between tensors are not saved)
+        assert torch.equal(store.m[off:off + p.numel()], store2.m[off:off + p.numel()])
+
+
+def test_metric_variants():
+    rs = np.random.RandomState(0)
+    n = 2000
+    pred = torch.from_numpy(rs.rand(n).astype(np.float32))
+    label = (torch.from_numpy(rs.rand(n).astype(np.float32)) < pred).float()
+    mask = torch.from_numpy((rs.rand(n) < 0.5).astype(np.int64))
+    cm = torch.from_numpy(rs.choice([222, 223], n))
+    rk = torch.from_numpy(rs.choice([1, 2, 3], n))
+    cmatch_rank = (cm << 32) | rk
+    t = {"pred": pred, "label": label, "mask": mask, "cmatch_rank": cmatch_rank, "m2": (mask * 2),
+         "pred_b": pred * 0.5, "uid": torch.from_numpy(rs.randint(0, 50, n))}
+    base = create_metric("AucCalculator", name="a", bucket_size=10000)
+    base.add_data(t)
+    full = base.get_metric_msg()
+    assert full[7] == n and 0.6 < full[0] < 0.9
+    mm = create_metric("MaskAucCalculator", name="m", mask_varname="mask", bucket_size=10000)
+    mm.add_data(t)
+    assert mm.get_metric_msg()[7] == int(mask.sum())
+    mu = create_metric("MultiMaskAucCalculator", name="mu", mask_varname="mask m2", mask_varvalue_list="1 2",
+                       bucket_size=10000)
+    mu.add_data(t)
+    assert mu.get_metric_msg()[7] == int(mask.sum())
+    cr = create_metric("CmatchRankAucCalculator", name="c", cmatch_rank_group="222_1 223_2",
+                       cmatch_rank_varname="cmatch_rank", bucket_size=10000)
+    cr.add_data(t)
+    exp = int((((cm == 222) & (rk == 1)) | ((cm == 223) & (rk == 2))).sum())
+    assert cr.get_metric_msg()[7] == exp
+    ci = create_metric("CmatchRankAucCalculator", name="ci", cmatch_rank_group="222", ignore_rank=True,
+                       cmatch_rank_varname="cmatch_rank", bucket_size=10000)
+    ci.add_data(t)
+    assert ci.get_metric_msg()[7] == int((cm == 222).sum())
+    crm = create_metric("CmatchRankMaskAucCalculator", name="crm", cmatch_rank_group="222_1", mask_varname="mask",
+                        cmatch_rank_varname="cmatch_rank", bucket_size=10000)
+    crm.add_data(t)
+    assert crm.get_metric_msg()[7] == int(((cm == 222) & (rk == 1) & (mask != 0)).sum())
+    mt = create_metric("MultiTaskAucCalculator", name="mt", pred_varname="pred pred_b",
+                       cmatch_rank_group="222_1 223_1", cmatch_rank_varname="cmatch_rank", bucket_size=10000)
+    mt.add_data(t)
+    assert mt.get_metric_msg()[7] == int(((rk == 1)).sum())
+    fm = create_metric("FloatMaskAucCalculator", name="f", mask_varname="mask", bucket_size=10000)
+    fm.add_data({**t, "label": pred})     # float labels
+    assert abs(fm.get_metric_msg()[7] - int(mask.sum())) < 1e-6
+    cont = create_metric("ContinueMaskCalculator", name="co", mask_varname="mask", bucket_size=10000)
+    cont.add_data({**t, "label": pred})
+    mae, rmse, pm, am, size = cont.get_metric_msg()
+    assert mae < 1e-6 and size == int(mask.sum())
+    wu = create_metric("WuAucCalculator", name="w", uid_varname="uid")
+    wu.add_data(t)
+    uauc, wuauc, users, size = wu.get_metric_msg()
+    assert users > 10 and 0.5 < wuauc < 1.0
+    ni = create_metric("NanInfCalculator", name="n")
+    ni.add_data({"pred": torch.tensor([0.1, float("nan"), float("inf")]), "label": torch.zeros(3)})
+    assert ni.get_nan_inf_msg() == [1, 1, 3]
+    with pytest.raises(ValueError):
+        create_metric("NoSuchCalculator", name="x")
+
+
+def test_rank_attention_matches_numpy_oracle():
+    rs = np.random.RandomState(1)
+    n, C, out, max_rank = 6, 4, 5, 3
+    x = rs.rand(n, C).astype(np.float32)
+    param = rs.rand(max_rank * max_rank * C, out).astype(np.float32)
+    sid = torch.tensor([7, 7, 7, 9, 9, 11])
+    rk = torch.tensor([1, 2, 3, 2, 1, 5])          # rank 5 > max_rank: ignored
+    ro = O.build_rank_offset(sid, rk, max_rank)
+    assert ro[0].tolist() == [1, 1, 0, 2, 1, 3, 2] and ro[5, 0] == -1
+    got = O.rank_attention(torch.from_numpy(x), ro, torch.from_numpy(param), max_rank)
+    # oracle restated from the reference's numpy test (test_rank_attention_op.py:25-108)
+    exp = np.zeros((n, out), np.float32)
+    for i in range(n):
+        lower = ro[i, 0].item() - 1
+        for k in range(max_rank):
+            faster = ro[i, 2 * k + 1].item() - 1
+            if lower < 0 or faster < 0:
+                continue
+            idx = ro[i, 2 * k + 2].item()
+            blk = param[(lower * max_rank + faster) * C:(lower * max_rank + faster + 1) * C]
+            exp[i] += x[idx] @ blk
+    assert np.allclose(got.numpy(), exp, rtol=1e-5, atol=1e-6)
+    xt = torch.from_numpy(x).requires_grad_(True)
+    O.rank_attention(xt, ro, torch.from_numpy(param), max_rank).sum().backward()
+    assert xt.grad is not None and xt.grad.abs().sum() > 0
+
+
+def test_batch_fc_scaled_fc_cross_norm_and_slices():
+    torch.manual_seed(0)
+    x = torch.rand(4, 6, 5)
+    w, b = torch.rand(4, 5, 3), torch.rand(4, 3)
+    exp = torch.stack([x[s] @ w[s] + b[s] for s in range(4)])
+    assert torch.allclose(O.batch_fc(x, w, b), exp, atol=1e-6)
+    assert O.BatchFC(4, 5, 3)(x).shape == torch.Size([4, 6, 3])
+    xi, wi, bi = torch.randn(8, 16, requires_grad=True), torch.randn(16, 4, requires_grad=True), torch.randn(4)
+    y = O.scaled_fc(xi, wi, bi, input_scale_factor=2.0, bias_scale_factor=0.5)
+    assert torch.allclose(y, (2 * xi) @ wi + 0.5 * bi, rtol=3e-2, atol=3e-2)
+    y.sum().backward()
+    assert torch.allclose(xi.grad, (torch.ones(8, 4) @ wi.t()) * 2, rtol=3e-2, atol=3e-2)
+    assert O.scaled_int8fc(xi.detach(), wi.detach(), bi).shape == (8, 4)
+    cn = O.CrossNormHadamard(fields_num=2, embed_dim=3)
+    out = cn(torch.rand(5, 12))
+    assert out.shape == (5, 18)
+    a, b2 = torch.arange(12.).reshape(3, 4), torch.arange(12., 24.).reshape(3, 4)
+    assert torch.equal(O.partial_concat([a, b2], 1, 2), torch.cat([a[:, 1:3], b2[:, 1:3]], 1))
+    assert torch.equal(O.partial_sum([a, b2], 1, 2), a[:, 1:3] + b2[:, 1:3])
+    assert torch.equal(O.fused_concat([a, b2], 2, -1), torch.cat([a[:, 2:], b2[:, 2:]], 1))
+    sh, idx = O.shuffle_batch(a, seed=3)
+    assert torch.equal(sh, a[idx]) and sorted(idx.tolist()) == [0, 1, 2]
+    kept, imap, w8 = O.filter_by_instag(a, [0, 1, 3, 4], torch.tensor([5, 6, 7, 8]), [7])
+    assert torch.equal(kept, a[1:2]) and imap.tolist() == [[0, 1]]
+    none, _, lw = O.filter_by_instag(a, [0, 1, 3, 4], torch.tensor([5, 6, 7, 8]), [99])
+    assert none.shape == (1, 4) and lw.item() == 0
+
+
+def test_seqpool_autograd_wrapper_and_variants_cpu():
+    gen = torch.Generator().manual_seed(0)
+    B, S, H = 5, 3, 7
+    lens = torch.randint(0, 4, (S * B,), generator=gen)
+    lod = torch.zeros(S * B + 1, dtype=torch.int32)
+    lod[1:] = torch.cumsum(lens, 0)
+    x = (torch.rand(int(lod[-1]), H, generator=gen) * 3).requires_grad_(True)
+    cvm = torch.rand(B, 2, generator=gen)
+    out = fused_seqpool_cvm(x, cvm, lod, B, S)
+    assert out.shape == (B, S * H) and len(split_slots(out, S)) == S
+    out.sum().backward()
+    # gradient: first two columns carry the cvm input, the rest ones
+    g = x.grad
+    assert torch.all(g[:, 2:] == 1)
+    b_of_k = torch.repeat_interleave(torch.arange(S * B) % B, lens)
+    assert torch.allclose(g[:, :2], cvm[b_of_k])
+    pc = O.fused_seqpool_cvm_with_pcoc(x.detach(), lod, B, S, cvm_offset=4)
+    assert pc.shape == (B, S * H)
+
+
+def test_side_tables_and_file_mgr(tmp_path):
+    c = GpuReplicaCache(4)
+    for i in range(5):
+        assert c.add_items([i, i + 1, i + 2, i + 3]) == i
+    c.to_hbm(torch.device("cpu"))
+    got = c.pull_cache_value(torch.tensor([4, 0]))
+    assert got.tolist() == [[4, 5, 6, 7], [0, 1, 2, 3]]
+    t = InputTable(2)
+    t.add_index_data("ad_1", [1.0, 2.0])
+    idxf = tmp_path / "idx.txt"
+    idxf.write_text("ad_2\t3 4\nbad\t1\n")
+    assert t.load_index_file(str(idxf)) == 1
+    offs = torch.tensor([t.get_index_offset("ad_2"), t.get_index_offset("nope"), t.get_index_offset("ad_1")])
+    assert t.lookup_input(offs).tolist() == [[3, 4], [0, 0], [1, 2]] and t.miss == 1
+    fm = BoxFileMgr()
+    d = str(tmp_path / "fs")
+    assert fm.makedir(d) and fm.exists(d)
+    fm.touch(os.path.join(d, "a"))
+    open(os.path.join(d, "b"), "w").write("hello")
+    assert fm.count(d) == 2 and fm.file_size(os.path.join(d, "b")) == 5
+    fm.rename(os.path.join(d, "b"), os.path.join(d, "c"))
+    fm.truncate(os.path.join(d, "c"), 2)
+    fm.upload(os.path.join(d, "c"), os.path.join(d, "e"))
+    assert sorted(os.path.basename(p) for p in fm.list_dir(d)) == ["a", "c", "e"]
+    assert dict((os.path.basename(p), s) for p, s in fm.dus(d))["e"] == 2
+    fm.remove(d)
+    assert not fm.exists(d)
+
+
+def test_boxps_optimizer_and_data_generator(tmp_path):
+    from paddlebox_b200.models.ctr import CtrDnn
+    from paddlebox_b200.optimizer import Adam, BoxPSOptimizer, LocalSGD
+    m = CtrDnn(num_slots=2, embedx_dim=4, dense_dim=1, hidden=(8,))
+    cfg = BoxPSOptimizer(Adam(learning_rate=0.01), sync_steps=4, sync_dense_mode=1).minimize(m)
+    assert cfg.dense_lr == 0.01 and cfg.sync_dense_mode == "kstep" and cfg.sync_weight_step == 4
+    assert m._pipeline_opt is cfg and "tower.weights.0" in m._param_need_sync
+    assert LocalSGD(k_steps=8).transpile(main_program=m) == "kstep" and cfg.sync_weight_step == 8
+    from paddlebox_b200.data_generator import MultiSlotDataGenerator
+
+    class G(MultiSlotDataGenerator):
+        def generate_sample(self, line):
+            def it():
+                a, b = line.split()
+                yield [("label", [float(a)]), ("slot", [int(b), int(b) + 1])]
+            return it
+    out = tmp_path / "gen.txt"
+    with open(out, "w") as f:
+        G().run_from_iterable(["1 5", "0 9"], f)
+    assert out.read_text() == "1 1.0 2 5 6\n1 0.0 2 9 10\n"
+
+
+def test_data_norm_module_updates_summaries():
+    dn = F.DataNorm(3, summary_decay_rate=0.5)
+    x = torch.tensor([[1., 2., 3.], [3., 2., 1.]], requires_grad=True)
+    y = dn(x)
+    y.sum().backward()
+    assert torch.allclose(dn.batch_size, torch.full((3,), 1e4 * 0.5 + 1))
+    assert torch.allclose(dn.batch_sum, torch.tensor([2., 2., 2.]))
+    assert torch.allclose(x.grad, torch.ones(2, 3) * torch.sqrt(torch.tensor(1e4 / 1e4)))
