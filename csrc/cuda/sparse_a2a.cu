@@ -23,7 +23,7 @@
 #include <vector>
 namespace cg = cooperative_groups;
 
-#define PBX_A2A_THREADS 512
+#define PBX_A2A_THREADS 1024
 
 struct PbxPullArgs {
   const uint64_t* keys;
@@ -326,9 +326,9 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
       for (int64_t j = gtid; j < (int64_t)cnt; j += gstride) {
         uint32_t row = mrow[j];
         if (row == PBX_NO_ROW) continue;
-        // the key comes from the table itself: a faster peer may already be overwriting
-        // this rank's key mailbox with the next batch
-        pbx_apply_push_fast(c.table, row, c.table.keys[row], pm + j * PD);
+        // (when the key is needed — lazy embedx creation — it is read from the table itself: a
+        // faster peer may already be overwriting this rank's key mailbox with the next batch)
+        pbx_apply_push_fast(c.table, row, pm + j * PD);
       }
     }
     if (s + 1 < R) grid.sync();

@@ -166,78 +166,96 @@ __device__ __forceinline__ void pbx_apply_push(const PbxTableView& t, uint32_t s
   if (t.dirty) t.dirty[slot_idx] = 1;
 }
 
-// Register-resident Adagrad update for a compile-time embedx width: the whole row (stride
-// = ceil4(9 + D) words) and the push record are moved with 16-byte loads/stores and the math
-// runs on registers.  Same arithmetic and order as pbx_apply_push (Adagrad branch).
-template <int D>
-__device__ __forceinline__ void pbx_apply_push_adagrad_vec(const PbxTableView& t, uint32_t slot_idx, uint64_t key,
-                                                           const float* __restrict__ push) {
-  constexpr int S4 = (9 + D + 3) / 4;
-  constexpr int P4 = (4 + D + 3) / 4;
-  constexpr int OFF_MF = 3 + D, OFF_T = 4 + D, OFF_ES = 7 + D, OFF_XS = 8 + D;
-  float p[P4 * 4];
-#pragma unroll
-  for (int i = 0; i < P4; ++i) {
-    float4 v = __ldcg(reinterpret_cast<const float4*>(push) + i);
-    p[4 * i] = v.x; p[4 * i + 1] = v.y; p[4 * i + 2] = v.z; p[4 * i + 3] = v.w;
-  }
-  const float g_show = p[1], g_click = p[2];
+// Streaming Adagrad update for embedx widths that are multiples of 4: the row and the push
+// record move as 16-byte vectors, but only a sliding window (one row chunk, two push chunks)
+// plus the three state-carrying chunks live in registers, so the kernels that call it keep a
+// small register footprint (-> 1024 threads per SM for latency hiding).  Same arithmetic and
+// accumulation order as pbx_apply_push (Adagrad branch).
+//
+// Word map (D = embedx dim): row  [show clk w x0 | x1..x4 | ... | x(D-3) x(D-2) x(D-1) mf |
+//                                  delta slot unseen g2 | xg2 pad pad pad]
+//                            push [slot gshow gclk gw | g0..g3 | g4..g7 | ...]
+// so embedx element e sits at row word 3+e and its gradient at push word 4+e: row chunk k
+// needs push chunk k lanes 1..3 and push chunk k+1 lane 0.
+__device__ __forceinline__ void pbx_apply_push_adagrad_stream(const PbxTableView& t, uint32_t slot_idx,
+                                                              const float* __restrict__ push) {
+  const int D = t.L.embedx_dim;
+  const int q = D >> 2;                       // chunk holding x(D-3..D-1), mf
+  const int S4 = t.L.stride >> 2;
+  const float4* pv = reinterpret_cast<const float4*>(push);
+  const float4 p0 = __ldcg(pv);               // slot, g_show, g_click, embed_g
+  const float g_show = p0.y, g_click = p0.z;
   if (g_show <= 0.f) return;
   float4* rowv = reinterpret_cast<float4*>(t.vals + (uint64_t)slot_idx * (S4 * 4));
-  float r[S4 * 4];
-#pragma unroll
-  for (int i = 0; i < S4; ++i) {
-    float4 v = rowv[i];
-    r[4 * i] = v.x; r[4 * i + 1] = v.y; r[4 * i + 2] = v.z; r[4 * i + 3] = v.w;
-  }
+  float4 r0 = rowv[0];
+  float4 rA = rowv[q];                        // x(D-3), x(D-2), x(D-1), mf_size
+  float4 rB = rowv[q + 1];                    // delta_score, slot, unseen_days, embed g2sum
+  float4 rC = rowv[q + 2];                    // embedx g2sum, pad
   const PbxSparseOptConfig& c = t.cfg;
-  r[OFF_T + 1] = p[0];
-  const float show = r[0] + g_show, click = r[1] + g_click;
-  r[0] = show;
-  r[1] = click;
-  r[OFF_T + 0] += c.nonclk_coeff * (g_show - g_click) + c.clk_coeff * g_click;
-  r[OFF_T + 2] = 0.f;
+  const float show = r0.x + g_show, click = r0.y + g_click;
+  r0.x = show;
+  r0.y = click;
+  rB.x += c.nonclk_coeff * (g_show - g_click) + c.clk_coeff * g_click;
+  rB.y = p0.x;
+  rB.z = 0.f;
   const float inv = 1.f / g_show;
-  {  // embed_w
-    float ratio = c.learning_rate * sqrtf(c.initial_g2sum / (c.initial_g2sum + r[OFF_ES]));
-    float sg = p[3] * inv;
-    r[2] = fminf(fmaxf(r[2] + sg * ratio, c.min_bound), c.max_bound);
-    r[OFF_ES] += sg * sg;
+  {
+    const float ratio = c.learning_rate * sqrtf(c.initial_g2sum / (c.initial_g2sum + rB.w));
+    const float sg = p0.w * inv;
+    r0.z = fminf(fmaxf(r0.z + sg * ratio, c.min_bound), c.max_bound);
+    rB.w += sg * sg;
   }
-  if (r[OFF_MF] == 0.f) {
+  if (rA.w == 0.f) {
     if (c.mf_create_thresholds <= c.nonclk_coeff * (show - click) + c.clk_coeff * click) {
-      r[OFF_MF] = (float)D;
-#pragma unroll
-      for (int i = 0; i < D; ++i) r[3 + i] = pbx_uniform01(key, (uint32_t)i, t.seed) * c.mf_initial_range;
+      // lazy embedx creation; the key is only needed here (counter-based RNG)
+      const uint64_t key = t.keys[slot_idx];
+      const float rg = c.mf_initial_range;
+      rA.w = (float)D;
+      r0.w = pbx_uniform01(key, 0u, t.seed) * rg;
+      for (int k = 1; k < q; ++k)
+        rowv[k] = make_float4(pbx_uniform01(key, 4 * k - 3, t.seed) * rg, pbx_uniform01(key, 4 * k - 2, t.seed) * rg,
+                              pbx_uniform01(key, 4 * k - 1, t.seed) * rg, pbx_uniform01(key, 4 * k, t.seed) * rg);
+      rA.x = pbx_uniform01(key, D - 3, t.seed) * rg;
+      rA.y = pbx_uniform01(key, D - 2, t.seed) * rg;
+      rA.z = pbx_uniform01(key, D - 1, t.seed) * rg;
     }
   } else {
-    float ratio = c.mf_learning_rate * sqrtf(c.mf_initial_g2sum / (c.mf_initial_g2sum + r[OFF_XS]));
+    const float ratio = c.mf_learning_rate * sqrtf(c.mf_initial_g2sum / (c.mf_initial_g2sum + rC.x));
+    const float lo = c.mf_min_bound, hi = c.mf_max_bound;
     float add = 0.f;
-#pragma unroll
-    for (int i = 0; i < D; ++i) {
-      float sg = p[4 + i] * inv;
-      r[3 + i] = fminf(fmaxf(r[3 + i] + sg * ratio, c.mf_min_bound), c.mf_max_bound);
-      add += sg * sg;
+    float4 pk = __ldcg(pv + 1);               // g0..g3
+    float sg = pk.x * inv;
+    r0.w = fminf(fmaxf(r0.w + sg * ratio, lo), hi);
+    add += sg * sg;
+    for (int k = 1; k < q; ++k) {
+      const float4 pn = __ldcg(pv + 1 + k);
+      float4 rk = rowv[k];
+      sg = pk.y * inv; rk.x = fminf(fmaxf(rk.x + sg * ratio, lo), hi); add += sg * sg;
+      sg = pk.z * inv; rk.y = fminf(fmaxf(rk.y + sg * ratio, lo), hi); add += sg * sg;
+      sg = pk.w * inv; rk.z = fminf(fmaxf(rk.z + sg * ratio, lo), hi); add += sg * sg;
+      sg = pn.x * inv; rk.w = fminf(fmaxf(rk.w + sg * ratio, lo), hi); add += sg * sg;
+      rowv[k] = rk;
+      pk = pn;
     }
-    r[OFF_XS] += add / (float)D;
+    sg = pk.y * inv; rA.x = fminf(fmaxf(rA.x + sg * ratio, lo), hi); add += sg * sg;
+    sg = pk.z * inv; rA.y = fminf(fmaxf(rA.y + sg * ratio, lo), hi); add += sg * sg;
+    sg = pk.w * inv; rA.z = fminf(fmaxf(rA.z + sg * ratio, lo), hi); add += sg * sg;
+    rC.x += add / (float)D;
   }
-#pragma unroll
-  for (int i = 0; i < S4; ++i) rowv[i] = make_float4(r[4 * i], r[4 * i + 1], r[4 * i + 2], r[4 * i + 3]);
+  rowv[0] = r0;
+  rowv[q] = rA;
+  rowv[q + 1] = rB;
+  rowv[q + 2] = rC;
   if (t.dirty) t.dirty[slot_idx] = 1;
 }
 
-// dispatch: vectorised Adagrad for the common widths, generic scalar path otherwise
-__device__ __forceinline__ void pbx_apply_push_fast(const PbxTableView& t, uint32_t slot_idx, uint64_t key,
-                                                    const float* push) {
-  if (t.L.optimizer == PBX_OPT_ADAGRAD) {
-    switch (t.L.embedx_dim) {
-      case 8: pbx_apply_push_adagrad_vec<8>(t, slot_idx, key, push); return;
-      case 16: pbx_apply_push_adagrad_vec<16>(t, slot_idx, key, push); return;
-      case 32: pbx_apply_push_adagrad_vec<32>(t, slot_idx, key, push); return;
-      default: break;   // wider rows would spill under the 128-register budget of 512-thread CTAs
-    }
+// dispatch: streaming vector path for Adagrad with D % 4 == 0 (D >= 4), generic scalar otherwise
+__device__ __forceinline__ void pbx_apply_push_fast(const PbxTableView& t, uint32_t slot_idx, const float* push) {
+  if (t.L.optimizer == PBX_OPT_ADAGRAD && t.L.embedx_dim >= 4 && (t.L.embedx_dim & 3) == 0) {
+    pbx_apply_push_adagrad_stream(t, slot_idx, push);
+    return;
   }
-  pbx_apply_push(t, slot_idx, key, push);
+  pbx_apply_push(t, slot_idx, t.keys[slot_idx], push);
 }
 
 // Host-side table object (opaque to callers; see include/pbx_cuda.h)

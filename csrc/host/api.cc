@@ -200,6 +200,9 @@ int64_t pbh_dataset_unique_keys(void* h, uint64_t* out, int64_t max_n) {
 }
 int pbh_dataset_save_archive(void* h, const char* path) { return ((Dataset*)h)->save_archive(path); }
 int pbh_dataset_load_archive(void* h, const char* path) { return ((Dataset*)h)->load_archive(path); }
+int pbh_dataset_save_partitioned(void* h, const char* prefix, int nparts, int mode, uint64_t seed) {
+  return ((Dataset*)h)->save_partitioned(prefix, nparts, mode, seed);
+}
 int64_t pbh_dataset_stats(void* h, char* buf, int64_t cap) {
   std::string s = ((Dataset*)h)->last_stats();
   if (buf && cap > 0) {

@@ -588,13 +588,13 @@ static const uint64_t kArchiveMagic = 0x50425841524348ull;  // "PBXARCH"
 template <typename T>
 static void put(std::string& buf, const T& v) { buf.append((const char*)&v, sizeof(T)); }
 
-int Dataset::save_archive(const std::string& path) const {
+static int write_archive(const std::string& path, const std::vector<const SlotRecord*>& recs) {
   FILE* fp = fopen(path.c_str(), "wb");
   PBH_REQUIRE(fp != nullptr, "cannot open %s for writing", path.c_str());
   std::string buf;
   put(buf, kArchiveMagic);
-  put(buf, (uint64_t)records_.size());
-  for (const SlotRecord* r : records_) {
+  put(buf, (uint64_t)recs.size());
+  for (const SlotRecord* r : recs) {
     put(buf, r->search_id); put(buf, r->rank); put(buf, r->cmatch);
     put(buf, (uint32_t)r->ins_id.size()); buf.append(r->ins_id);
     put(buf, (uint32_t)r->u64_vals.size());
@@ -609,6 +609,33 @@ int Dataset::save_archive(const std::string& path) const {
   }
   fwrite(buf.data(), 1, buf.size(), fp);
   fclose(fp);
+  return 0;
+}
+
+int Dataset::save_archive(const std::string& path) const {
+  std::vector<const SlotRecord*> all(records_.begin(), records_.end());
+  return write_archive(path, all);
+}
+
+// Global shuffle, sending side: split the records into `world` partition files
+// "<prefix>.<this rank>.<dst>" (the reference hash-partitions records to ranks and ships them
+// over the PaddleShuffler RPC: by search_id, by XXH64 of the ins_id, or randomly;
+// data_set.cc:2422-2547).  mode 0 = random, 1 = search_id, 2 = hash of ins_id.
+int Dataset::save_partitioned(const std::string& prefix, int nparts, int mode, uint64_t seed) const {
+  PBH_REQUIRE(nparts >= 1, "nparts must be >= 1");
+  std::vector<std::vector<const SlotRecord*>> parts(nparts);
+  std::mt19937_64 rng(seed + (uint64_t)rank * 0x9E3779B97F4A7C15ull);
+  for (const SlotRecord* r : records_) {
+    uint64_t h;
+    if (mode == 1) h = mix64(r->search_id);
+    else if (mode == 2) h = mix64(std::hash<std::string>()(r->ins_id.substr(0, 32)));
+    else h = rng();
+    parts[h % (uint64_t)nparts].push_back(r);
+  }
+  for (int d = 0; d < nparts; ++d) {
+    int rc = write_archive(prefix + "." + std::to_string(rank) + "." + std::to_string(d), parts[d]);
+    if (rc) return rc;
+  }
   return 0;
 }
 

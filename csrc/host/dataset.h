@@ -120,6 +120,7 @@ class Dataset {
   int64_t total_feasigns() const { return total_feasigns_.load(); }
   // ---- archive (binary spill / reload; preload_into_disk) ----
   int save_archive(const std::string& path) const;
+  int save_partitioned(const std::string& prefix, int nparts, int mode, uint64_t seed) const;
   int load_archive(const std::string& path);
   std::string last_stats() const;
 

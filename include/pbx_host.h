@@ -44,6 +44,8 @@ int64_t pbh_dataset_batch_ins_ids(void* ds, int worker, int64_t b, char* buf, in
 int64_t pbh_dataset_unique_keys(void* ds, uint64_t* out, int64_t max_n);
 int pbh_dataset_save_archive(void* ds, const char* path);
 int pbh_dataset_load_archive(void* ds, const char* path);
+/* global shuffle, sending side: partition files "<prefix>.<rank>.<dst>"; mode 0 random, 1 search_id, 2 ins_id hash */
+int pbh_dataset_save_partitioned(void* ds, const char* prefix, int nparts, int mode, uint64_t seed);
 int64_t pbh_dataset_stats(void* ds, char* buf, int64_t cap);
 int pbh_dataset_parse_line(void* ds, const char* line, int64_t* n_u64, int64_t* n_f32, uint64_t* u64_out,
                            int64_t u64_cap, float* f32_out, int64_t f32_cap, uint64_t* search_id);
