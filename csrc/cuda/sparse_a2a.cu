@@ -23,7 +23,11 @@
 #include <vector>
 namespace cg = cooperative_groups;
 
+// pull: 1024 threads (61 registers, no spills) for latency hiding; push: 512 threads so that the
+// software-pipelined optimizer phase can keep four rows per lane group in registers
 #define PBX_A2A_THREADS 1024
+#define PBX_PUSH_THREADS 512
+#define PBX_PUSH_SMEM ((PBX_PUSH_THREADS / 32) * (32 * 36 + 32 * 24) * 4)   /* Q3 warp tiles */
 
 struct PbxPullArgs {
   const uint64_t* keys;
@@ -51,6 +55,9 @@ struct PbxPushArgs {
   float grad_scale;         // -batch_size (box_wrapper.cu:404-410)
 };
 struct PbxPushArgsN { PbxPushArgs a[PBX_MAX_RANKS]; };
+
+// phase timestamps (one thread, globaltimer) for benchmarks/micro.py --phases; slots live after the epoch word
+#define PBX_TS(i) do { if (lb == 0 && tid == 0) c.epoch[16 + (i)] = pbx_globaltimer(); } while (0)
 
 namespace {
 
@@ -93,6 +100,7 @@ k_sparse_pull(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPullArgsN args)
   const uint32_t cap = c.cap;
   const int tid = threadIdx.x;
   const uint64_t e0 = *c.epoch;
+  PBX_TS(0);
 
   __shared__ uint32_t s_cnt[PBX_MAX_RANKS];
   __shared__ uint32_t s_base[PBX_MAX_RANKS];
@@ -100,6 +108,7 @@ k_sparse_pull(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPullArgsN args)
   // ---- P0: reset per-batch counters (dedup table was cleaned by the previous pull)
   if (lb == 0 && tid < R) c.send_cnt[tid] = 0;
   grid.sync();
+  PBX_TS(1);
 
   // ---- P1: dedup + claim a mailbox slot per unique key + ship the key to its owner
   {
@@ -148,6 +157,7 @@ k_sparse_pull(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPullArgsN args)
     }
   }
   grid.sync();
+  PBX_TS(2);
 
   // ---- P2: occurrence -> unique row, publish counts, clean the dedup table
   {
@@ -161,12 +171,14 @@ k_sparse_pull(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPullArgsN args)
     }
   }
   grid.sync();  // all reads of dd_uid done before dd_keys is recycled
+  PBX_TS(3);
   {
     const int64_t stride = (int64_t)bpr * PBX_A2A_THREADS;
     for (int64_t i = (int64_t)lb * PBX_A2A_THREADS + tid; i < (int64_t)c.dd_cap; i += stride)
       c.dd_keys[i] = PBX_EMPTY_KEY;
   }
   xbarrier<EMU>(grid, c, e0 + 1, lb == 0);
+  PBX_TS(4);
 
   // ---- P3: owner side — probe the local shard, return rows into the requester's buffer
   {
@@ -208,11 +220,12 @@ k_sparse_pull(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPullArgsN args)
     }
   }
   xbarrier<EMU>(grid, c, e0 + 2, lb == 0);
+  PBX_TS(5);
   if (lb == 0 && tid == 0) *c.epoch = e0 + 2;
 }
 
 template <bool EMU>
-__global__ void __launch_bounds__(PBX_A2A_THREADS, 1)
+__global__ void __launch_bounds__(PBX_PUSH_THREADS, 1)
 k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args) {
   cg::grid_group grid = cg::this_grid();
   const int bpr = gridDim.x / nvr;
@@ -225,9 +238,10 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
   const int tid = threadIdx.x;
   const int PD = c.push_stride;
   const int pchunks = PD >> 2;
-  const int64_t gtid = (int64_t)lb * PBX_A2A_THREADS + tid;
-  const int64_t gstride = (int64_t)bpr * PBX_A2A_THREADS;
+  const int64_t gtid = (int64_t)lb * PBX_PUSH_THREADS + tid;
+  const int64_t gstride = (int64_t)bpr * PBX_PUSH_THREADS;
   const uint64_t e0 = *c.epoch;
+  PBX_TS(8);
 
   // ---- Q0: zero the merge rows in use
   for (int o = 0; o < R; ++o) {
@@ -236,6 +250,7 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
     for (int64_t it = gtid; it < items; it += gstride) base[it] = make_float4(0.f, 0.f, 0.f, 0.f);
   }
   grid.sync();
+  PBX_TS(9);
 
   // ---- Q1: merge by unique key (fused with the seqpool/CVM backward in mode 0)
   if (a.mode == 0 && a.cvm_offset == 2) {
@@ -303,6 +318,7 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
     }
   }
   grid.sync();
+  PBX_TS(10);
 
   // ---- Q2: ship merged records to their owners
   for (int o = 0; o < R; ++o) {
@@ -313,6 +329,7 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
     for (int64_t it = gtid; it < items; it += gstride) dst[it] = src[it];
   }
   xbarrier<EMU>(grid, c, e0 + 1, lb == 0);
+  PBX_TS(11);
 
   // ---- Q3: owner applies the optimizer; one requester at a time so that a key pushed by
   // several ranks is updated once per rank without a race (reference applies per-GPU
@@ -323,16 +340,67 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
       const float* pm = s == c.rank ? c.push_acc + (uint64_t)s * cap * PD
                                     : c.push_mail[c.rank] + (uint64_t)s * cap * PD;
       const uint32_t* mrow = c.mail_row + (uint64_t)s * cap;
-      for (int64_t j = gtid; j < (int64_t)cnt; j += gstride) {
-        uint32_t row = mrow[j];
-        if (row == PBX_NO_ROW) continue;
-        // (when the key is needed — lazy embedx creation — it is read from the table itself: a
-        // faster peer may already be overwriting this rank's key mailbox with the next batch)
-        pbx_apply_push_fast(c.table, row, pm + j * PD);
+      const PbxTableView& T = c.table;
+      if (T.L.stride == 32 && PD <= 24) {
+        // Warp-tile path (rows of one 128-byte line, every optimizer): a warp takes 32 records,
+        // loads their rows with coalesced 128-byte requests (8 lanes x 16 B per row) into shared
+        // memory, ONE lane per row runs the optimizer functor on the shared copy, and the rows
+        // go back with coalesced stores.  Memory sees whole lines and many independent requests;
+        // the math is not replicated across lanes (the 8-lanes-per-row variants were issue-bound).
+        extern __shared__ float4 s_q3[];
+        constexpr int RS = 36;                       // padded row stride in words: conflict-free float4
+        const int lane = tid & 31, wib = tid >> 5;
+        float* s_rows = reinterpret_cast<float*>(s_q3) + wib * (32 * RS + 32 * 24);
+        float* s_push = s_rows + 32 * RS;
+        const int64_t warp = (int64_t)lb * (PBX_PUSH_THREADS / 32) + wib;
+        const int64_t nwarps = (int64_t)bpr * (PBX_PUSH_THREADS / 32);
+        const int sub = lane & 7, rq = lane >> 3;
+        for (int64_t j0 = warp * 32; j0 < (int64_t)cnt; j0 += nwarps * 32) {
+          const int nvalid = (int)min((int64_t)32, (int64_t)cnt - j0);
+          const uint32_t myrow = lane < nvalid ? __ldg(mrow + j0 + lane) : PBX_NO_ROW;
+          float4 rv[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {              // all eight row loads in flight before any use
+            const uint32_t r = __shfl_sync(0xffffffffu, myrow, rq + 4 * i);
+            rv[i] = r != PBX_NO_ROW ? *reinterpret_cast<const float4*>(T.vals + (uint64_t)r * 32 + 4 * sub)
+                                    : make_float4(0.f, 0.f, 0.f, 0.f);
+          }
+          const float4* psrc = reinterpret_cast<const float4*>(pm + j0 * PD);
+          const int pvec = nvalid * (PD >> 2);
+          for (int idx = lane; idx < pvec; idx += 32)
+            reinterpret_cast<float4*>(s_push)[idx] = __ldcg(psrc + idx);
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            *reinterpret_cast<float4*>(s_rows + (rq + 4 * i) * RS + 4 * sub) = rv[i];
+          __syncwarp();
+          bool touched = false;
+          if (myrow != PBX_NO_ROW) touched = pbx_apply_push_ptr(T, s_rows + lane * RS, myrow, s_push + lane * PD);
+          __syncwarp();
+          const unsigned tmask = __ballot_sync(0xffffffffu, touched);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int rr = rq + 4 * i;
+            const uint32_t r = __shfl_sync(0xffffffffu, myrow, rr);
+            if ((tmask >> rr) & 1u)
+              *reinterpret_cast<float4*>(T.vals + (uint64_t)r * 32 + 4 * sub) =
+                  *reinterpret_cast<const float4*>(s_rows + rr * RS + 4 * sub);
+          }
+          if (touched && T.dirty) T.dirty[myrow] = 1;
+          __syncwarp();
+        }
+      } else {
+        for (int64_t j = gtid; j < (int64_t)cnt; j += gstride) {
+          uint32_t row = mrow[j];
+          if (row == PBX_NO_ROW) continue;
+          // (when the key is needed — lazy embedx creation — it is read from the table itself: a
+          // faster peer may already be overwriting this rank's key mailbox with the next batch)
+          pbx_apply_push_fast(T, row, pm + j * PD);
+        }
       }
     }
     if (s + 1 < R) grid.sync();
   }
+  PBX_TS(12);
   if (lb == 0 && tid == 0) *c.epoch = e0 + 1;
 }
 
@@ -424,6 +492,10 @@ int pbx_sparse_create(void** out, void* table, int rank, int nranks, int64_t max
   int bps = 0;
   PBX_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_sparse_pull<false>, PBX_A2A_THREADS, 0));
   PBX_REQUIRE(bps >= 1, "sparse pull kernel does not fit on an SM");
+  PBX_CUDA_CHECK(cudaFuncSetAttribute(k_sparse_push<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      PBX_PUSH_SMEM));
+  PBX_CUDA_CHECK(cudaFuncSetAttribute(k_sparse_push<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      PBX_PUSH_SMEM));
   c->grid_blocks = pbx_num_sms();
   PBX_CUDA_CHECK(cudaDeviceSynchronize());
   *out = c;
@@ -514,6 +586,14 @@ static int pbx_ctx_sync_dev(PbxSparseCtx* c, cudaStream_t st) {
   return 0;
 }
 
+// copies the 16 phase timestamps (ns, globaltimer) of the last pull [0..5] and push [8..12]
+int pbx_sparse_phase_times(void* hnd, uint64_t* out16, cudaStream_t st) {
+  PbxSparseCtx* c = (PbxSparseCtx*)hnd;
+  PBX_CUDA_CHECK(cudaMemcpyAsync(out16, c->h.epoch + 16, 16 * sizeof(uint64_t), cudaMemcpyDeviceToHost, st));
+  PBX_CUDA_CHECK(cudaStreamSynchronize(st));
+  return 0;
+}
+
 int pbx_sparse_status(void* hnd, int* status, int reset, cudaStream_t st) {
   PbxSparseCtx* c = (PbxSparseCtx*)hnd;
   PBX_CUDA_CHECK(cudaMemcpyAsync(status, c->h.status, sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -598,7 +678,7 @@ int pbx_sparse_push_ex(void* hnd, const uint32_t* d_restore, int64_t n, const fl
   int nvr = 1;
   void* kargs[] = {(void*)&dctx, (void*)&nvr, (void*)&args};
   PBX_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_sparse_push<false>, dim3(c->grid_blocks),
-                                             dim3(PBX_A2A_THREADS), kargs, 0, st));
+                                             dim3(PBX_PUSH_THREADS), kargs, PBX_PUSH_SMEM, st));
   pbx_note_launch(1);
   return 0;
 }
@@ -655,8 +735,8 @@ int pbx_sparse_push_emu(void* const* hnds, int nranks, const uint32_t* const* d_
   if (bpr < 1) bpr = 1;
   const PbxSparseDev* dctx = d;
   void* kargs[] = {(void*)&dctx, (void*)&nranks, (void*)&args};
-  cudaError_t e = cudaLaunchCooperativeKernel((void*)k_sparse_push<true>, dim3(bpr * nranks), dim3(PBX_A2A_THREADS),
-                                              kargs, 0, st);
+  cudaError_t e = cudaLaunchCooperativeKernel((void*)k_sparse_push<true>, dim3(bpr * nranks), dim3(PBX_PUSH_THREADS),
+                                              kargs, PBX_PUSH_SMEM, st);
   if (e == cudaSuccess) e = cudaStreamSynchronize(st);
   cudaFree(d);
   PBX_CUDA_CHECK(e);

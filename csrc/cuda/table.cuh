@@ -18,6 +18,7 @@ struct PbxTableView {
   PbxRowLayout L;
   PbxSparseOptConfig cfg;
   int test_mode;      // 1: pushes are ignored (reference SetTestMode)
+  int dbg;            // PBX_DBG env: perf experiments only (bit0 no dirty mark, bit1 no row stores, bit2 no embedx loop)
 };
 
 __device__ __forceinline__ uint32_t pbx_dev_find(const PbxTableView& t, uint64_t key) {
@@ -112,14 +113,15 @@ __device__ __forceinline__ void pbx_adam(float* w, float* m, float* v, float* b1
   *b2p = b2pow * b2;
 }
 
-// Apply one merged push record to one row.  push = [slot, show, click, embed_g, embedx_g[D]].
-__device__ __forceinline__ void pbx_apply_push(const PbxTableView& t, uint32_t slot_idx, uint64_t key,
-                                               const float* push) {
+// Apply one merged push record to one row held at `row` (global or shared memory).
+// push = [slot, show, click, embed_g, embedx_g[D]].  Returns false when the record is empty.
+// The key (needed only for lazy embedx creation) is read from the table on demand.
+__device__ __forceinline__ bool pbx_apply_push_ptr(const PbxTableView& t, float* row, uint32_t slot_idx,
+                                                   const float* push) {
   const PbxRowLayout& L = t.L;
   const PbxSparseOptConfig& c = t.cfg;
-  float* row = t.vals + (uint64_t)slot_idx * L.stride;
   float g_show = push[1], g_click = push[2];
-  if (g_show <= 0.f) return;  // nothing merged into this record
+  if (g_show <= 0.f) return false;  // nothing merged into this record
   row[L.off_tail + 1] = push[0];  // slot
   float show = row[0] + g_show;
   float click = row[1] + g_click;
@@ -139,6 +141,7 @@ __device__ __forceinline__ void pbx_apply_push(const PbxTableView& t, uint32_t s
   if (row[L.off_mf] == 0.f) {
     // lazy embedx creation (optimizer.cuh.h:104-122)
     if (c.mf_create_thresholds <= c.nonclk_coeff * (show - click) + c.clk_coeff * click) {
+      const uint64_t key = t.keys[slot_idx];
       row[L.off_mf] = (float)D;
       for (int i = 0; i < D; ++i) row[3 + i] = pbx_uniform01(key, (uint32_t)i, t.seed) * c.mf_initial_range;
       if (L.optimizer == PBX_OPT_ADAM) {
@@ -163,7 +166,15 @@ __device__ __forceinline__ void pbx_apply_push(const PbxTableView& t, uint32_t s
                true);
     }
   }
-  if (t.dirty) t.dirty[slot_idx] = 1;
+  return true;
+}
+
+// in-place update of the table row `slot_idx` (generic path; `key` kept for API stability)
+__device__ __forceinline__ void pbx_apply_push(const PbxTableView& t, uint32_t slot_idx, uint64_t key,
+                                               const float* push) {
+  (void)key;
+  if (pbx_apply_push_ptr(t, t.vals + (uint64_t)slot_idx * t.L.stride, slot_idx, push) && t.dirty)
+    t.dirty[slot_idx] = 1;
 }
 
 // Streaming Adagrad update for embedx widths that are multiples of 4: the row and the push
@@ -219,7 +230,7 @@ __device__ __forceinline__ void pbx_apply_push_adagrad_stream(const PbxTableView
       rA.y = pbx_uniform01(key, D - 2, t.seed) * rg;
       rA.z = pbx_uniform01(key, D - 1, t.seed) * rg;
     }
-  } else {
+  } else if (!(t.dbg & 4)) {
     const float ratio = c.mf_learning_rate * sqrtf(c.mf_initial_g2sum / (c.mf_initial_g2sum + rC.x));
     const float lo = c.mf_min_bound, hi = c.mf_max_bound;
     float add = 0.f;
@@ -242,11 +253,13 @@ __device__ __forceinline__ void pbx_apply_push_adagrad_stream(const PbxTableView
     sg = pk.w * inv; rA.z = fminf(fmaxf(rA.z + sg * ratio, lo), hi); add += sg * sg;
     rC.x += add / (float)D;
   }
-  rowv[0] = r0;
-  rowv[q] = rA;
-  rowv[q + 1] = rB;
-  rowv[q + 2] = rC;
-  if (t.dirty) t.dirty[slot_idx] = 1;
+  if (!(t.dbg & 2)) {
+    rowv[0] = r0;
+    rowv[q] = rA;
+    rowv[q + 1] = rB;
+    rowv[q + 2] = rC;
+  }
+  if (!(t.dbg & 1) && t.dirty) t.dirty[slot_idx] = 1;
 }
 
 // dispatch: streaming vector path for Adagrad with D % 4 == 0 (D >= 4), generic scalar otherwise

@@ -670,6 +670,8 @@ int Dataset::load_archive(const std::string& path) {
   fclose(fp);
   PBH_REQUIRE(ok, "archive %s is truncated or not a paddlebox_b200 archive", path.c_str());
   if (collect_keys) {
+    // several archives may be loaded into one pass (global shuffle): keep the union of their keys
+    agent_.add_keys(unique_keys_.data(), unique_keys_.size());
     ThreadPool pool(std::max(1, merge_thread_num));
     agent_.finalize(&pool, &unique_keys_);
     agent_.clear();

@@ -81,7 +81,10 @@ static inline PbxRowLayout pbx_make_layout(int embedx_dim, int optimizer) {
   l.off_es = l.off_tail + 3;
   l.off_xs = l.off_es + l.embed_state;
   int words = l.off_xs + l.embedx_state;
-  l.stride = (words + 3) / 4 * 4;
+  /* rows are padded to whole 128-byte lines: a row (and its read-modify-write by the optimizer)
+   * then touches the minimum number of DRAM lines; random-line throughput, not bandwidth, bounds
+   * the sparse kernels */
+  l.stride = (words + 31) / 32 * 32;
   l.pull_stride = (3 + embedx_dim + 3) / 4 * 4;
   l.push_stride = (4 + embedx_dim + 3) / 4 * 4;
   return l;

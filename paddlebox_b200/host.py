@@ -354,6 +354,10 @@ class NativeDataset:
     def load_archive(self, path: str):
         N.hcheck(N.host().pbh_dataset_load_archive(self._h, path.encode()))
 
+    def save_partitioned(self, prefix: str, nparts: int, mode: int = 0, seed: int = 0):
+        """Write ``<prefix>.<rank>.<dst>`` partition files (mode 0 random, 1 search_id, 2 ins_id)."""
+        N.hcheck(N.host().pbh_dataset_save_partitioned(self._h, prefix.encode(), nparts, mode, C.c_uint64(seed)))
+
     def stats(self) -> str:
         buf = C.create_string_buffer(1024)
         N.host().pbh_dataset_stats(self._h, buf, C.c_int64(1024))
