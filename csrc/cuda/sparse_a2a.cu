@@ -331,74 +331,108 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
   xbarrier<EMU>(grid, c, e0 + 1, lb == 0);
   PBX_TS(11);
 
-  // ---- Q3: owner applies the optimizer; one requester at a time so that a key pushed by
-  // several ranks is updated once per rank without a race (reference applies per-GPU
-  // pushes one after another under the table write lock, heter_comm_inl.h:1779-1804).
-  for (int s = 0; s < R; ++s) {
-    const uint32_t cnt = c.serve_cnt[s];
-    if (!c.table.test_mode) {
+  // ---- Q3: owner applies the fused sparse optimizer.
+  // Rows of one 128-byte line (every optimizer): WARP TILES over the flattened list of all
+  // requesters' records — a warp takes 32 records of one requester, loads their rows with
+  // coalesced 128-byte requests (8 lanes x 16 B per row) into shared memory, ONE lane per row
+  // runs the optimizer functor on the shared copy, and the rows go back with coalesced stores.
+  // A key pushed by several requesters is serialised by a try-lock in the spare last word of its
+  // row (no hold-and-wait: a lane that loses the race retries after the warp has released its
+  // own locks), which replaces the reference's "one GPU at a time under the table write lock"
+  // (heter_comm_inl.h:1779-1804) without a grid barrier per requester.
+  const PbxTableView& T = c.table;
+  if (T.test_mode) {
+    // pushes are ignored in test mode
+  } else if (T.L.stride == 32 && PD <= 24) {
+    extern __shared__ float4 s_q3[];
+    constexpr int RS = 36;                       // padded row stride in words: conflict-free float4
+    const int lane = tid & 31, wib = tid >> 5;
+    float* s_rows = reinterpret_cast<float*>(s_q3) + wib * (32 * RS + 32 * 24);
+    float* s_push = s_rows + 32 * RS;
+    const int64_t warp = (int64_t)lb * (PBX_PUSH_THREADS / 32) + wib;
+    const int64_t nwarps = (int64_t)bpr * (PBX_PUSH_THREADS / 32);
+    const int sub = lane & 7, rq = lane >> 3;
+    const bool locking = R > 1;
+    int64_t tile_base = 0;                       // tiles of requester s are [tile_base, tile_base + ntiles)
+    for (int s = 0; s < R; ++s) {
+      const uint32_t cnt = c.serve_cnt[s];
+      const int64_t ntiles = ((int64_t)cnt + 31) >> 5;
       const float* pm = s == c.rank ? c.push_acc + (uint64_t)s * cap * PD
                                     : c.push_mail[c.rank] + (uint64_t)s * cap * PD;
       const uint32_t* mrow = c.mail_row + (uint64_t)s * cap;
-      const PbxTableView& T = c.table;
-      if (T.L.stride == 32 && PD <= 24) {
-        // Warp-tile path (rows of one 128-byte line, every optimizer): a warp takes 32 records,
-        // loads their rows with coalesced 128-byte requests (8 lanes x 16 B per row) into shared
-        // memory, ONE lane per row runs the optimizer functor on the shared copy, and the rows
-        // go back with coalesced stores.  Memory sees whole lines and many independent requests;
-        // the math is not replicated across lanes (the 8-lanes-per-row variants were issue-bound).
-        extern __shared__ float4 s_q3[];
-        constexpr int RS = 36;                       // padded row stride in words: conflict-free float4
-        const int lane = tid & 31, wib = tid >> 5;
-        float* s_rows = reinterpret_cast<float*>(s_q3) + wib * (32 * RS + 32 * 24);
-        float* s_push = s_rows + 32 * RS;
-        const int64_t warp = (int64_t)lb * (PBX_PUSH_THREADS / 32) + wib;
-        const int64_t nwarps = (int64_t)bpr * (PBX_PUSH_THREADS / 32);
-        const int sub = lane & 7, rq = lane >> 3;
-        for (int64_t j0 = warp * 32; j0 < (int64_t)cnt; j0 += nwarps * 32) {
-          const int nvalid = (int)min((int64_t)32, (int64_t)cnt - j0);
-          const uint32_t myrow = lane < nvalid ? __ldg(mrow + j0 + lane) : PBX_NO_ROW;
+      // first tile of this requester owned by this warp (global round-robin over all tiles)
+      int64_t t0 = (warp - tile_base % nwarps + nwarps) % nwarps;
+      for (int64_t tl = t0; tl < ntiles; tl += nwarps) {
+        const int64_t j0 = tl * 32;
+        const int nvalid = (int)min((int64_t)32, (int64_t)cnt - j0);
+        const uint32_t myrow = lane < nvalid ? __ldg(mrow + j0 + lane) : PBX_NO_ROW;
+        const float4* psrc = reinterpret_cast<const float4*>(pm + j0 * PD);
+        const int pvec = nvalid * (PD >> 2);
+        for (int idx = lane; idx < pvec; idx += 32)
+          reinterpret_cast<float4*>(s_push)[idx] = __ldcg(psrc + idx);
+        bool pending = myrow != PBX_NO_ROW;
+        while (__any_sync(0xffffffffu, pending)) {
+          bool got = pending;
+          if (locking && pending) {
+            unsigned int* lk = reinterpret_cast<unsigned int*>(T.vals + (uint64_t)myrow * 32 + 31);
+            got = atomicCAS(lk, 0u, 1u) == 0u;
+            if (got) __threadfence();            // acquire: row reads below must see the previous owner's stores
+          }
+          const unsigned gmask = __ballot_sync(0xffffffffu, got);
           float4 rv[8];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {              // all eight row loads in flight before any use
-            const uint32_t r = __shfl_sync(0xffffffffu, myrow, rq + 4 * i);
-            rv[i] = r != PBX_NO_ROW ? *reinterpret_cast<const float4*>(T.vals + (uint64_t)r * 32 + 4 * sub)
-                                    : make_float4(0.f, 0.f, 0.f, 0.f);
+          for (int i = 0; i < 8; ++i) {          // all eight row loads in flight before any use
+            const int rr = rq + 4 * i;
+            const uint32_t r = __shfl_sync(0xffffffffu, myrow, rr);
+            rv[i] = ((gmask >> rr) & 1u) ? __ldcg(reinterpret_cast<const float4*>(T.vals + (uint64_t)r * 32 + 4 * sub))
+                                         : make_float4(0.f, 0.f, 0.f, 0.f);
           }
-          const float4* psrc = reinterpret_cast<const float4*>(pm + j0 * PD);
-          const int pvec = nvalid * (PD >> 2);
-          for (int idx = lane; idx < pvec; idx += 32)
-            reinterpret_cast<float4*>(s_push)[idx] = __ldcg(psrc + idx);
 #pragma unroll
           for (int i = 0; i < 8; ++i)
             *reinterpret_cast<float4*>(s_rows + (rq + 4 * i) * RS + 4 * sub) = rv[i];
           __syncwarp();
           bool touched = false;
-          if (myrow != PBX_NO_ROW) touched = pbx_apply_push_ptr(T, s_rows + lane * RS, myrow, s_push + lane * PD);
+          if (got) touched = pbx_apply_push_ptr(T, s_rows + lane * RS, myrow, s_push + lane * PD);
           __syncwarp();
           const unsigned tmask = __ballot_sync(0xffffffffu, touched);
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const int rr = rq + 4 * i;
             const uint32_t r = __shfl_sync(0xffffffffu, myrow, rr);
+            // (the lock word, lane 7 / word 3 of the last chunk, is written back as "held": its
+            //  shared copy was loaded after the lock was taken; the release below clears it)
             if ((tmask >> rr) & 1u)
               *reinterpret_cast<float4*>(T.vals + (uint64_t)r * 32 + 4 * sub) =
                   *reinterpret_cast<const float4*>(s_rows + rr * RS + 4 * sub);
           }
           if (touched && T.dirty) T.dirty[myrow] = 1;
+          if (locking) {
+            __threadfence();                     // release: the row stores above before the unlock
+            __syncwarp();
+            if (got) atomicExch(reinterpret_cast<unsigned int*>(T.vals + (uint64_t)myrow * 32 + 31), 0u);
+          }
+          if (got) pending = false;
           __syncwarp();
         }
-      } else {
-        for (int64_t j = gtid; j < (int64_t)cnt; j += gstride) {
-          uint32_t row = mrow[j];
-          if (row == PBX_NO_ROW) continue;
-          // (when the key is needed — lazy embedx creation — it is read from the table itself: a
-          // faster peer may already be overwriting this rank's key mailbox with the next batch)
-          pbx_apply_push_fast(T, row, pm + j * PD);
-        }
       }
+      tile_base += ntiles;
     }
-    if (s + 1 < R) grid.sync();
+  } else {
+    // generic path (wide rows): one requester at a time, separated by grid barriers
+    for (int s = 0; s < R; ++s) {
+      const uint32_t cnt = c.serve_cnt[s];
+      const float* pm = s == c.rank ? c.push_acc + (uint64_t)s * cap * PD
+                                    : c.push_mail[c.rank] + (uint64_t)s * cap * PD;
+      const uint32_t* mrow = c.mail_row + (uint64_t)s * cap;
+      for (int64_t j = gtid; j < (int64_t)cnt; j += gstride) {
+        uint32_t row = mrow[j];
+        if (row == PBX_NO_ROW) continue;
+        // (when the key is needed — lazy embedx creation — it is read from the table itself: a
+        // faster peer may already be overwriting this rank's key mailbox with the next batch)
+        pbx_apply_push_fast(T, row, pm + j * PD);
+      }
+      if (s + 1 < R) grid.sync();
+    }
   }
   PBX_TS(12);
   if (lb == 0 && tid == 0) *c.epoch = e0 + 1;

@@ -84,7 +84,7 @@ static inline PbxRowLayout pbx_make_layout(int embedx_dim, int optimizer) {
   /* rows are padded to whole 128-byte lines: a row (and its read-modify-write by the optimizer)
    * then touches the minimum number of DRAM lines; random-line throughput, not bandwidth, bounds
    * the sparse kernels */
-  l.stride = (words + 31) / 32 * 32;
+  l.stride = (words + 1 + 31) / 32 * 32;   /* + 1: the last word of a row is its update lock */
   l.pull_stride = (3 + embedx_dim + 3) / 4 * 4;
   l.push_stride = (4 + embedx_dim + 3) / 4 * 4;
   return l;

@@ -68,7 +68,7 @@ def make_layout(embedx_dim: int, optimizer: int) -> RowLayout:
     l.off_es = l.off_tail + 3
     l.off_xs = l.off_es + l.embed_state
     words = l.off_xs + l.embedx_state
-    l.stride = (words + 31) // 32 * 32      # whole 128-byte lines (see pbx_types.h)
+    l.stride = (words + 1 + 31) // 32 * 32  # whole 128-byte lines; last word = row lock (see pbx_types.h)
     l.pull_stride = (3 + embedx_dim + 3) // 4 * 4
     l.push_stride = (4 + embedx_dim + 3) // 4 * 4
     return l
