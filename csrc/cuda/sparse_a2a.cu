@@ -27,7 +27,9 @@ namespace cg = cooperative_groups;
 // software-pipelined optimizer phase can keep four rows per lane group in registers
 #define PBX_A2A_THREADS 1024
 #define PBX_PUSH_THREADS 512
-#define PBX_PUSH_SMEM ((PBX_PUSH_THREADS / 32) * (32 * 36 + 32 * 24) * 4)   /* Q3 warp tiles */
+#define PBX_PUSH_SMEM ((PBX_PUSH_THREADS / 32) * (32 * 36 + 32 * 24) * 4)   /* Q3 warp tiles, one-line rows */
+#define PBX_PUSH_WIDE_WARP_WORDS 3200                                        /* Q3 warp tiles, wide rows */
+#define PBX_PUSH_SMEM_WIDE ((PBX_PUSH_THREADS / 32) * PBX_PUSH_WIDE_WARP_WORDS * 4)
 
 struct PbxPullArgs {
   const uint64_t* keys;
@@ -417,8 +419,89 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
       }
       tile_base += ntiles;
     }
+  } else if (c.q3_tile_rows >= 2) {
+    // Rows of several 128-byte lines: the same warp-tile scheme with TR (< 32) rows per tile —
+    // the row and its push record are staged with coalesced 16-byte accesses, lanes [0, TR) run
+    // the optimizer functor on the shared copy, the tile is written back coalesced.
+    extern __shared__ float4 s_q3[];
+    const int ST = T.L.stride, RS = ST + 4, SV = ST >> 2, TR = c.q3_tile_rows;
+    const int lane = tid & 31, wib = tid >> 5;
+    float* s_rows = reinterpret_cast<float*>(s_q3) + (size_t)wib * c.q3_warp_words;
+    float* s_push = s_rows + TR * RS;
+    const int64_t warp = (int64_t)lb * (PBX_PUSH_THREADS / 32) + wib;
+    const int64_t nwarps = (int64_t)bpr * (PBX_PUSH_THREADS / 32);
+    const bool locking = R > 1;
+    const int nvec = TR * SV;
+    int64_t tile_base = 0;
+    for (int s = 0; s < R; ++s) {
+      const uint32_t cnt = c.serve_cnt[s];
+      const int64_t ntiles = ((int64_t)cnt + TR - 1) / TR;
+      const float* pm = s == c.rank ? c.push_acc + (uint64_t)s * cap * PD
+                                    : c.push_mail[c.rank] + (uint64_t)s * cap * PD;
+      const uint32_t* mrow = c.mail_row + (uint64_t)s * cap;
+      int64_t t0 = (warp - tile_base % nwarps + nwarps) % nwarps;
+      for (int64_t tl = t0; tl < ntiles; tl += nwarps) {
+        const int64_t j0 = tl * TR;
+        const int nvalid = (int)min((int64_t)TR, (int64_t)cnt - j0);
+        const uint32_t myrow = lane < nvalid ? __ldg(mrow + j0 + lane) : PBX_NO_ROW;
+        const float4* psrc = reinterpret_cast<const float4*>(pm + j0 * PD);
+        const int pvec = nvalid * (PD >> 2);
+        for (int idx = lane; idx < pvec; idx += 32)
+          reinterpret_cast<float4*>(s_push)[idx] = __ldcg(psrc + idx);
+        bool pending = myrow != PBX_NO_ROW;
+        while (__any_sync(0xffffffffu, pending)) {
+          bool got = pending;
+          if (locking && pending) {
+            unsigned int* lk = reinterpret_cast<unsigned int*>(T.vals + (uint64_t)myrow * ST + ST - 1);
+            got = atomicCAS(lk, 0u, 1u) == 0u;
+            if (got) __threadfence();
+          }
+          const unsigned gmask = __ballot_sync(0xffffffffu, got);
+          for (int base = 0; base < nvec; base += 128) {   // 4 independent 16-byte loads per lane in flight
+            float4 rv[4];
+            int rr[4], ch[4];
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int idx = base + i * 32 + lane;
+              rr[i] = min(idx / SV, TR - 1);
+              ch[i] = idx - rr[i] * SV;
+              const uint32_t r = __shfl_sync(0xffffffffu, myrow, rr[i]);
+              rv[i] = (idx < nvec && ((gmask >> rr[i]) & 1u))
+                          ? __ldcg(reinterpret_cast<const float4*>(T.vals + (uint64_t)r * ST) + ch[i])
+                          : make_float4(0.f, 0.f, 0.f, 0.f);
+            }
+#pragma unroll
+            for (int i = 0; i < 4; ++i)
+              if (base + i * 32 + lane < nvec) *reinterpret_cast<float4*>(s_rows + rr[i] * RS + 4 * ch[i]) = rv[i];
+          }
+          __syncwarp();
+          bool touched = false;
+          if (got) touched = pbx_apply_push_ptr(T, s_rows + lane * RS, myrow, s_push + lane * PD);
+          __syncwarp();
+          const unsigned tmask = __ballot_sync(0xffffffffu, touched);
+          for (int base = 0; base < nvec; base += 32) {
+            const int idx = base + lane;
+            const int rr = min(idx / SV, TR - 1);
+            const int ch = idx - rr * SV;
+            const uint32_t r = __shfl_sync(0xffffffffu, myrow, rr);
+            if (idx < nvec && ((tmask >> rr) & 1u))
+              *(reinterpret_cast<float4*>(T.vals + (uint64_t)r * ST) + ch) =
+                  *reinterpret_cast<const float4*>(s_rows + rr * RS + 4 * ch);
+          }
+          if (touched && T.dirty) T.dirty[myrow] = 1;
+          if (locking) {
+            __threadfence();
+            __syncwarp();
+            if (got) atomicExch(reinterpret_cast<unsigned int*>(T.vals + (uint64_t)myrow * ST + ST - 1), 0u);
+          }
+          if (got) pending = false;
+          __syncwarp();
+        }
+      }
+      tile_base += ntiles;
+    }
   } else {
-    // generic path (wide rows): one requester at a time, separated by grid barriers
+    // generic path (rows too wide for a shared-memory tile): one requester at a time, separated by grid barriers
     for (int s = 0; s < R; ++s) {
       const uint32_t cnt = c.serve_cnt[s];
       const float* pm = s == c.rank ? c.push_acc + (uint64_t)s * cap * PD
@@ -457,6 +540,10 @@ struct PbxSparseCtx {
   int grid_blocks;         // cooperative grid size (per real rank)
   void* table;             // PbxTable*
 };
+
+static size_t pbx_push_smem(const PbxSparseDev& h) {
+  return h.q3_tile_rows == 0 ? 0 : (size_t)(PBX_PUSH_THREADS / 32) * h.q3_warp_words * 4;
+}
 
 static void pbx_ctx_bind_peer(PbxSparseCtx* c, int p, void* base) {
   char* b = (char*)base;
@@ -527,9 +614,24 @@ int pbx_sparse_create(void** out, void* table, int rank, int nranks, int64_t max
   PBX_CUDA_CHECK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&bps, k_sparse_pull<false>, PBX_A2A_THREADS, 0));
   PBX_REQUIRE(bps >= 1, "sparse pull kernel does not fit on an SM");
   PBX_CUDA_CHECK(cudaFuncSetAttribute(k_sparse_push<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      PBX_PUSH_SMEM));
+                                      PBX_PUSH_SMEM_WIDE));
   PBX_CUDA_CHECK(cudaFuncSetAttribute(k_sparse_push<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      PBX_PUSH_SMEM));
+                                      PBX_PUSH_SMEM_WIDE));
+  // push Q3 tiling: one-line rows use 32-row tiles; wider rows use the largest power-of-two
+  // tile that fits the per-warp shared-memory share; rows too wide for 2 per warp fall back
+  // to the per-thread path
+  {
+    const int st = t->view.L.stride, pd = h.push_stride;
+    if (st == 32 && pd <= 24) {
+      h.q3_tile_rows = 32;
+      h.q3_warp_words = 32 * 36 + 32 * 24;
+    } else {
+      int tr = 32;
+      while (tr >= 2 && tr * (st + 4 + pd) > PBX_PUSH_WIDE_WARP_WORDS) tr >>= 1;
+      h.q3_tile_rows = tr >= 2 ? tr : 0;
+      h.q3_warp_words = PBX_PUSH_WIDE_WARP_WORDS;
+    }
+  }
   c->grid_blocks = pbx_num_sms();
   PBX_CUDA_CHECK(cudaDeviceSynchronize());
   *out = c;
@@ -712,7 +814,7 @@ int pbx_sparse_push_ex(void* hnd, const uint32_t* d_restore, int64_t n, const fl
   int nvr = 1;
   void* kargs[] = {(void*)&dctx, (void*)&nvr, (void*)&args};
   PBX_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_sparse_push<false>, dim3(c->grid_blocks),
-                                             dim3(PBX_PUSH_THREADS), kargs, PBX_PUSH_SMEM, st));
+                                             dim3(PBX_PUSH_THREADS), kargs, pbx_push_smem(c->h), st));
   pbx_note_launch(1);
   return 0;
 }
@@ -770,7 +872,7 @@ int pbx_sparse_push_emu(void* const* hnds, int nranks, const uint32_t* const* d_
   const PbxSparseDev* dctx = d;
   void* kargs[] = {(void*)&dctx, (void*)&nranks, (void*)&args};
   cudaError_t e = cudaLaunchCooperativeKernel((void*)k_sparse_push<true>, dim3(bpr * nranks), dim3(PBX_PUSH_THREADS),
-                                              kargs, PBX_PUSH_SMEM, st);
+                                              kargs, pbx_push_smem(hs[0]), st);
   if (e == cudaSuccess) e = cudaStreamSynchronize(st);
   cudaFree(d);
   PBX_CUDA_CHECK(e);

@@ -26,5 +26,7 @@ struct PbxSparseDev {
   float* push_acc;      // [nranks*cap*push_stride] local merge buffer
   uint64_t* epoch;      // barrier epoch counter
   int* status;          // 0 ok, 1 mailbox overflow, 2 barrier timeout
+  int q3_tile_rows;     // push Q3: rows per warp tile (0 = generic per-thread path)
+  int q3_warp_words;    // push Q3: shared-memory words per warp
   PbxTableView table;
 };

@@ -178,17 +178,19 @@ def test_sparse_push_explicit_key_grads():
         assert torch.allclose(amap[k], exp_row, rtol=1e-3, atol=1e-4)
 
 
-@pytest.mark.parametrize("nranks", [2, 4, 8])
-def test_sparse_pull_push_virtual_ranks(nranks):
+@pytest.mark.parametrize("nranks,dim,opt", [(2, 8, "adagrad"), (4, 8, "adagrad"), (8, 8, "adagrad"),
+                                             (2, 64, "adagrad"), (4, 8, "adam"), (2, 40, "shared_adam"),
+                                             (2, 200, "adam")])
+def test_sparse_pull_push_virtual_ranks(nranks, dim, opt):
     """All ranks as virtual ranks of one cooperative launch: the production per-rank code,
     sharded tables, cross-rank mailboxes — checked against a single global oracle."""
     from paddlebox_b200.ops.sparse_table import SparseTable
     from paddlebox_b200.parallel.sparse_engine import EmulatedSparseGroup
     gen = torch.Generator().manual_seed(11)
-    B, S, dim = 48, 4, 8
+    B, S = 48, 4
     H = 3 + dim
-    tables = [_mk_table(cap=1 << 14, dim=dim) for _ in range(nranks)]
-    oracle = _mk_table(cap=1 << 16, dim=dim)
+    tables = [_mk_table(cap=1 << 14, dim=dim, opt=opt) for _ in range(nranks)]
+    oracle = _mk_table(cap=1 << 16, dim=dim, opt=opt)
     batches = [_bags(B, S, 5, 2000, gen) for _ in range(nranks)]
     batches = [(k.to(dev()), l.to(dev())) for k, l in batches]
     allk = torch.cat([k for k, _ in batches]).unique()
