@@ -94,6 +94,8 @@ def main():
             t_pull = timed(pull, a.iters, 3, dev)
             t_push = timed(push, a.iters, 3, dev)
             eng.check_status()
+            pull(); push()
+            phases = eng.phase_times()
             uk = torch.unique(keys)
             own = owner_of(uk.cpu().numpy().view("uint64"), world)
             remote = int((own != rank).sum())
@@ -112,6 +114,7 @@ def main():
                    "pull_roofline_us": round(roof_pull, 1), "push_roofline_us": round(roof_push, 1),
                    "pull_frac": round(roof_pull / t_pull, 3), "push_frac": round(roof_push / t_push, 3),
                    "pull_nvlink_GBps": round(nv_pull / t_pull / 1e3, 1), "push_nvlink_GBps": round(nv_push / t_push / 1e3, 1)}
+            rec["phases_us_rank0"] = phases
             if not a.no_nccl:
                 # ---- NCCL baseline of the same pull: unique -> a2a keys -> lookup -> a2a values -> gather
                 def nccl_pull():

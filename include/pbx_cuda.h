@@ -55,6 +55,8 @@ int pbx_sparse_connect_local(void* ctx, void* const* peers);
 int pbx_sparse_geometry(void* ctx, int64_t* cap, int64_t* n_unique_rows, int* pull_stride, int* push_stride);
 float* pbx_sparse_pull_values(void* ctx);
 int pbx_sparse_status(void* ctx, int* status, int reset, pbx_stream_t stream);
+/* Copies the 16 phase-boundary globaltimer stamps (ns) of the last pull (0..5) and push (8..12); synchronises. */
+int pbx_sparse_phase_times(void* ctx, uint64_t* out16, pbx_stream_t stream);
 int pbx_sparse_pull(void* ctx, const uint64_t* d_keys, int64_t n, uint32_t* d_restore, pbx_stream_t stream);
 /* d_n: optional device int32 with the real key count (n is then the upper bound) — graph-replay friendly */
 int pbx_sparse_pull_ex(void* ctx, const uint64_t* d_keys, int64_t n, const int32_t* d_n, uint32_t* d_restore,

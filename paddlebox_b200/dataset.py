@@ -313,6 +313,15 @@ class InMemoryDataset(DatasetBase):
         loader = _BatchLoader(self._native, w, device, prefetch, with_ins_id)
         return iter(loader)
 
+    def host_batches(self, worker: int | None = None, prefetch: int = 3, with_ins_id: bool = False):
+        """Iterate this worker's batches as pinned, record-major :class:`~paddlebox_b200.feed.HostBatch`
+        es (no device work): the input of the pipelined feed ``CTRTrainer.train_host_batches``."""
+        if self._prepared_workers == 0:
+            self.prepare_train(1)
+        w = self._worker if worker is None else worker
+        loader = _BatchLoader(self._native, w, torch.device("cuda"), prefetch, with_ins_id)
+        return loader.host_batches()
+
 
 class QueueDataset(InMemoryDataset):
     """Streaming flavour (reference ``QueueDataset``: no shuffle).  Here it loads file by file
@@ -463,6 +472,21 @@ class _BatchLoader:
                 self.q.put((b, B, n, st, ids))
         finally:
             self.q.put(None)
+
+    def host_batches(self):
+        """Packed batches left in pinned memory (the staging buffer returns to the pool when the
+        consumer calls ``HostBatch.release``)."""
+        from .feed import HostBatch
+        self.thread.start()
+        S, Dd = self.S, self.Dd
+        while True:
+            item = self.q.get()
+            if item is None:
+                return
+            b, B, n, st, ids = item
+            k, o, d = st.views(n, B * (S + 1), B * Dd)
+            yield HostBatch(k, o, d.view(B, Dd) if Dd else None, B, S, n, ins_ids=ids,
+                            release=lambda st=st: self.free.put(st))
 
     def __iter__(self):
         self.thread.start()

@@ -123,6 +123,19 @@ class SparseEngine:
         if st.value:
             raise RuntimeError(STATUS_MSG.get(st.value, f"sparse engine status {st.value}"))
 
+    PULL_PHASES = ("P0 reset", "P1 dedup+route keys", "P2 restore idx", "P2 clear dedup + barrier",
+                   "P3 serve rows + barrier")
+    PUSH_PHASES = ("Q0 zero merge rows", "Q1 merge (seqpool bwd)", "Q2 ship + barrier", "Q3 optimizer")
+
+    def phase_times(self) -> dict:
+        """Wall time (us) of every phase of the last pull and the last push on this rank, from
+        ``globaltimer`` stamps written by one thread at the phase boundaries (synchronises)."""
+        ts = (C.c_uint64 * 16)()
+        N.check(N.cuda().pbx_sparse_phase_times(self._h, ts, N.stream_ptr()), "pbx_sparse_phase_times")
+        t = [int(x) for x in ts]
+        return {"pull": {n: round((t[i + 1] - t[i]) / 1e3, 1) for i, n in enumerate(self.PULL_PHASES)},
+                "push": {n: round((t[9 + i] - t[8 + i]) / 1e3, 1) for i, n in enumerate(self.PUSH_PHASES)}}
+
 
 class EmulatedSparseGroup:
     """All ranks of a sparse group as *virtual ranks* of one cooperative launch on ONE GPU.

@@ -137,3 +137,37 @@ def test_model_families_train_on_gpu(tmp_path, gbox, cls, kw):
 def test_graft_smoke():
     import __graft_entry__ as ge
     ge.smoke()
+
+
+@pytest.mark.parametrize("graph", [False, True])
+def test_pipelined_feed_matches_plain_loop(tmp_path, graph):
+    """dataset.host_batches -> CTRTrainer.train_host_batches (copy stream + batch_build into the
+    step's buffers + loss ring) gives the same per-step losses as the plain loader loop."""
+    def run(pipelined):
+        BoxWrapper.reset_instance()
+        box = BoxWrapper.set_instance(embedx_dim=8, rank=0, world_size=1)
+        box.initialize_gpu_and_load_model({"mf_create_thresholds": 1.0}, table_capacity=1 << 16,
+                                          max_keys_per_batch=1 << 14)
+        torch.manual_seed(3)
+        ds = _ds(tmp_path, 6, 4, 128, 32, files=2)     # 256 instances -> 8 full batches
+        model = DeepFM(num_slots=6, embedx_dim=8, dense_dim=4, hidden=(32, 16)).cuda()
+        tr = CTRTrainer(model, box, TrainerConfig(dense_lr=1e-2))
+        ds.load_into_memory()
+        ds.begin_pass()
+        ds.prepare_train(1)
+        if graph:
+            first = next(iter(ds.batches()))
+            assert tr.enable_cuda_graph(first, 1 << 14, warmup=1)
+        if pipelined:
+            st = tr.train_host_batches(ds.host_batches())
+            losses = st["losses"]
+            assert st["h2d_bytes"] > 0 and st["d2h_bytes"] == 4 * st["steps"]
+        else:
+            losses = [float(tr.train_step(b).detach()) for b in ds.batches()]
+        box.engine.check_status()
+        ds.end_pass()
+        BoxWrapper.reset_instance()
+        return losses
+    a, b = run(False), run(True)
+    assert len(a) == len(b) == 8
+    assert np.allclose(a, b, rtol=2e-3, atol=2e-4), (a, b)
