@@ -163,6 +163,9 @@ int pbh_dataset_local_shuffle(void* h, uint64_t seed) { ((Dataset*)h)->local_shu
 int pbh_dataset_slots_shuffle(void* h, const int* slots, int n, uint64_t seed) {
   return ((Dataset*)h)->slots_shuffle(std::vector<int>(slots, slots + n), seed);
 }
+int pbh_dataset_slots_shuffle_back(void* h, const int* slots, int n, uint64_t seed) {
+  return ((Dataset*)h)->slots_shuffle(std::vector<int>(slots, slots + n), seed, true);
+}
 int pbh_dataset_prepare_train(void* h, int nworkers, int shuffle, uint64_t seed, int64_t min_batches) {
   return ((Dataset*)h)->prepare_train(nworkers, shuffle != 0, seed, min_batches);
 }

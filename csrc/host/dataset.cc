@@ -434,13 +434,18 @@ void Dataset::local_shuffle(uint64_t seed) {
 // AUC-runner: permute the feasigns of the chosen slots across records, keeping every other
 // slot in place, to measure how much the model relies on those slots
 // (reference RecordReplace / slots_shuffle, data_feed.h:1772-1962, box_wrapper.cc:212-368).
-int Dataset::slots_shuffle(const std::vector<int>& slot_idx, uint64_t seed) {
+int Dataset::slots_shuffle(const std::vector<int>& slot_idx, uint64_t seed, bool inverse) {
   const size_t n = records_.size();
   if (n < 2) return 0;
   std::vector<size_t> perm(n);
   for (size_t i = 0; i < n; ++i) perm[i] = i;
   std::mt19937_64 rng(seed);
   std::shuffle(perm.begin(), perm.end(), rng);
+  if (inverse) {  // undo a previous shuffle with the same seed (reference RecordReplaceBack)
+    std::vector<size_t> inv(n);
+    for (size_t i = 0; i < n; ++i) inv[perm[i]] = i;
+    perm.swap(inv);
+  }
   std::vector<char> chosen(n_used_u64_, 0);
   for (int s : slot_idx) {
     PBH_REQUIRE(s >= 0 && s < (int)slots.size() && slot_to_sparse_[s] >= 0, "slot %d is not a used sparse slot", s);

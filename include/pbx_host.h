@@ -29,6 +29,8 @@ int pbh_dataset_wait_preload_done(void* ds);
 int pbh_dataset_release_memory(void* ds);
 int pbh_dataset_local_shuffle(void* ds, uint64_t seed);
 int pbh_dataset_slots_shuffle(void* ds, const int* slots, int n, uint64_t seed);
+/* undoes pbh_dataset_slots_shuffle called with the same slots and seed */
+int pbh_dataset_slots_shuffle_back(void* ds, const int* slots, int n, uint64_t seed);
 int pbh_dataset_prepare_train(void* ds, int nworkers, int shuffle, uint64_t seed, int64_t min_batches);
 int64_t pbh_dataset_num_records(void* ds);
 int64_t pbh_dataset_num_batches(void* ds, int worker);

@@ -64,21 +64,21 @@ class BoxWrapper:
     @classmethod
     def set_instance(cls, embedx_dim: int = 8, expand_embed_dim: int = 0, feature_type: int = 0,
                      pull_embedx_scale: float = 1.0, **kw) -> "BoxWrapper":
-        if cls._instance is None:
-            cls._instance = cls(embedx_dim, expand_embed_dim, feature_type, pull_embedx_scale, **kw)
-        return cls._instance
+        if BoxWrapper._instance is None:      # one PS per process, whichever front end created it
+            BoxWrapper._instance = cls(embedx_dim, expand_embed_dim, feature_type, pull_embedx_scale, **kw)
+        return BoxWrapper._instance
 
     @classmethod
     def get_instance(cls) -> "BoxWrapper":
-        if cls._instance is None:
+        if BoxWrapper._instance is None:
             raise RuntimeError("BoxWrapper.set_instance(...) has not been called")
-        return cls._instance
+        return BoxWrapper._instance
 
     @classmethod
     def reset_instance(cls) -> None:
-        if cls._instance is not None:
-            cls._instance.finalize()
-        cls._instance = None
+        if BoxWrapper._instance is not None:
+            BoxWrapper._instance.finalize()
+        BoxWrapper._instance = None
 
     def __init__(self, embedx_dim: int = 8, expand_embed_dim: int = 0, feature_type: int = 0,
                  pull_embedx_scale: float = 1.0, *, optimizer: str = "adagrad", device: torch.device | None = None,
@@ -297,6 +297,33 @@ class BoxWrapper:
         """Merge another checkpoint into the host tier (``MergeModel``): loaded rows replace
         existing ones."""
         return self.host_table.load(path)
+
+    def merge_multi_models(self, paths, update_type: int = 0, idx: int = 0) -> int:
+        """``MergeMultiModels(path, update_type, idx)``: merge several checkpoints into the host
+        tier.  ``update_type`` 0: later models replace earlier rows; 1: show/click of rows present
+        in several models are summed (weights from the last); ``idx`` >= 0 with a single string
+        path selects ``<path>/<idx>``."""
+        import os
+        if isinstance(paths, str):
+            paths = [os.path.join(paths, str(idx))] if os.path.isdir(os.path.join(paths, str(idx))) else [paths]
+        n = 0
+        acc = {}
+        for p in paths:
+            if update_type == 1:
+                keys = self.host_table.keys()
+                if len(keys):
+                    rows = self.host_table.fetch_rows(keys, create=False)
+                    acc = {int(k): (float(r[0]), float(r[1])) for k, r in zip(keys, rows)}
+            n += self.host_table.load(p)
+            if update_type == 1 and acc:
+                keys = self.host_table.keys()
+                rows = self.host_table.fetch_rows(keys, create=False).copy()
+                for i, k in enumerate(keys.tolist()):
+                    if k in acc:
+                        rows[i, 0] += acc[k][0]
+                        rows[i, 1] += acc[k][1]
+                self.host_table.store_rows(keys, rows)
+        return n
 
     def set_test_mode(self, on: bool) -> None:
         self._test_mode = bool(on)

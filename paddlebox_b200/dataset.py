@@ -256,6 +256,11 @@ class InMemoryDataset(DatasetBase):
         names = [s.name for s in self.all_slots]
         self._native.slots_shuffle([names.index(s) for s in slots], self._shuffle_seed + 1)
 
+    def slots_shuffle_back(self, slots: Sequence[str]):
+        """Undo the last ``slots_shuffle(slots)`` (reference ``RecordReplaceBack``, data_feed.h:1772-1962)."""
+        names = [s.name for s in self.all_slots]
+        self._native.slots_shuffle_back([names.index(s) for s in slots], self._shuffle_seed + 1)
+
     def get_memory_data_size(self, fleet=None) -> int:
         return self._native.num_records()
 

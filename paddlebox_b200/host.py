@@ -298,6 +298,10 @@ class NativeDataset:
         n = len(slot_indices)
         N.hcheck(N.host().pbh_dataset_slots_shuffle(self._h, (C.c_int * n)(*slot_indices), n, C.c_uint64(seed)))
 
+    def slots_shuffle_back(self, slot_indices: Sequence[int], seed: int = 0):
+        n = len(slot_indices)
+        N.hcheck(N.host().pbh_dataset_slots_shuffle_back(self._h, (C.c_int * n)(*slot_indices), n, C.c_uint64(seed)))
+
     def prepare_train(self, nworkers: int, shuffle: bool = True, seed: int = 0, min_batches: int = 0):
         N.hcheck(N.host().pbh_dataset_prepare_train(self._h, nworkers, int(shuffle), C.c_uint64(seed),
                                                     C.c_int64(min_batches)))

@@ -199,3 +199,59 @@ def row_gather(table: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
     N.check(N.cuda().pbx_row_gather(N.ptr(table.contiguous()), N.ptr(idx), C.c_int64(idx.numel()), table.shape[1],
                                     N.ptr(out), N.stream_ptr()))
     return out
+
+
+# ---- masked_data_norm (operators/masked_data_norm_op.cu:39-307) ---------------------------------
+class _MaskedDataNorm(torch.autograd.Function):
+    """Rows with ``mask == 0`` produce zeros, receive no gradient and do not contribute to the
+    batch statistics; the summary "gradients" follow the GPU kernel: size 1 (0 if no row is
+    selected), mean of selected rows, mean squared deviation + epsilon."""
+
+    @staticmethod
+    def forward(ctx, x, mask, bsize, bsum, bsq, eps, stat_sink):
+        mean = bsum / bsize
+        scale = torch.sqrt(bsize / bsq)
+        m = mask.reshape(-1, 1).to(x.dtype)
+        y = (x - mean) * scale * m
+        ctx.save_for_backward(x, m, mean, scale)
+        ctx.eps, ctx.sink = eps, stat_sink
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, m, mean, scale = ctx.saved_tensors
+        dx = dy * scale * m
+        if ctx.sink is not None:
+            cnt = m.sum()
+            has = (cnt > 0).to(x.dtype)
+            denom = cnt.clamp(min=1.0)
+            d_size = torch.ones_like(mean) * has
+            d_sum = (x * m).sum(0) / denom * has
+            d_sq = ((((x - mean) ** 2) * m).sum(0) / denom + ctx.eps) * has
+            ctx.sink(d_size, d_sum, d_sq)
+        return dx, None, None, None, None, None, None
+
+
+def masked_data_norm(x, mask, batch_size, batch_sum, batch_square_sum, epsilon: float = 1e-4, stat_sink=None):
+    """``y[r] = mask[r] ? (x[r] - sum/size) * sqrt(size/square_sum) : 0``."""
+    return _MaskedDataNorm.apply(x, mask, batch_size, batch_sum, batch_square_sum, epsilon, stat_sink)
+
+
+# ---- store_q_value (operators/store_q_value_op.cc:36-96) ----------------------------------------
+_Q_STORE: dict = {}
+
+
+def store_q_value(q_tensors, batch=None, device_id: int | None = None) -> list:
+    """Copy the PCOC q tensors of the current batch to the host and park them on the batch
+    (and in a per-device store the next pack step reads), like ``BatchGpuPackMgr().store_qvalue``."""
+    host = [q.detach().to("cpu", non_blocking=False).contiguous() for q in q_tensors]
+    if device_id is None:
+        device_id = q_tensors[0].device.index or 0 if q_tensors[0].is_cuda else -1
+    _Q_STORE[device_id] = host
+    if batch is not None:
+        batch.q_values = host
+    return host
+
+
+def stored_q_values(device_id: int = 0) -> list:
+    return _Q_STORE.get(device_id, [])

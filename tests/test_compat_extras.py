@@ -1,0 +1,155 @@
+"""AUC runner (slot shuffle feature evaluation), cluster/thread helpers, HeterPS-flavoured names,
+masked_data_norm, store_q_value, merge_multi_models — all on CPU."""
+import numpy as np
+import pytest
+import torch
+
+from paddlebox_b200.auc_runner import AucRunner
+from paddlebox_b200.box_wrapper import BoxWrapper
+from paddlebox_b200.dataset import DatasetFactory
+from paddlebox_b200.models.ctr import CtrDnn
+from paddlebox_b200.ops import functional as F
+from paddlebox_b200.parallel import cluster
+from paddlebox_b200.trainer import CTRTrainer, TrainerConfig
+from tests.util_data import slot_vars, write_files
+
+
+@pytest.fixture
+def box():
+    BoxWrapper.reset_instance()
+    b = BoxWrapper.set_instance(embedx_dim=8, device=torch.device("cpu"), rank=0, world_size=1)
+    b.initialize_gpu_and_load_model({"mf_create_thresholds": 1.0, "learning_rate": 0.1, "mf_learning_rate": 0.1})
+    yield b
+    BoxWrapper.reset_instance()
+
+
+def _dataset(tmp_path, n_sparse=6, n_dense=3, lines=300):
+    ds = DatasetFactory().create_dataset("PadBoxSlotDataset")
+    ds.set_use_var(slot_vars(n_sparse, n_dense))
+    ds.set_batch_size(32)
+    ds.set_thread(2)
+    ds.set_filelist(write_files(str(tmp_path), n_files=2, lines_per_file=lines, n_sparse=n_sparse, n_dense=n_dense,
+                                key_space=40))
+    return ds
+
+
+def test_slots_shuffle_back_restores_records(tmp_path, box):
+    ds = _dataset(tmp_path)
+    ds.load_into_memory()
+    ds.begin_pass()
+    ds.prepare_train(1)
+    before = [b.keys.clone() for b in ds.batches()]
+    ds.slots_shuffle(["slot0", "slot3"])
+    during = [b.keys.clone() for b in ds.batches()]
+    ds.slots_shuffle_back(["slot0", "slot3"])
+    after = [b.keys.clone() for b in ds.batches()]
+    assert any(a.numel() != d.numel() or not torch.equal(a, d) for a, d in zip(before, during))
+    assert all(torch.equal(a, b) for a, b in zip(before, after))
+    ds.end_pass(False)
+
+
+def test_auc_runner_ranks_the_informative_slot(tmp_path, box):
+    torch.manual_seed(0)
+    ds = _dataset(tmp_path)
+    box.init_metric("AucCalculator", "auc", "label", "pred", metric_phase=1, bucket_size=100000)
+    model = CtrDnn(num_slots=6, embedx_dim=8, dense_dim=3, hidden=(32, 16))
+    tr = CTRTrainer(model, box, TrainerConfig(dense_lr=1e-2))
+    for _ in range(8):
+        ds.load_into_memory()
+        ds.begin_pass()
+        tr.train_from_dataset(ds)
+        ds.end_pass(False)
+        ds.release_memory()
+    box.get_metric_msg("auc")
+    ds.load_into_memory()
+    ds.begin_pass()
+    shows_before = box.host_table.fetch_rows(box.host_table.keys(), create=False)[:, 0].sum()
+    runner = AucRunner(box, [["slot0"], ["slot4"]], metric="auc",
+                       slot_list=[f"slot{i}" for i in range(6)])
+    res = runner.run(tr, ds)
+    ds.end_pass(False)
+    assert res["base"] > 0.7
+    drop0, drop4 = res["groups"][0]["drop"], res["groups"][1]["drop"]
+    assert drop0 > 0.1 and drop0 > drop4 + 0.05          # the clicks depend on slot0 only
+    # evaluation ran in test mode: nothing was pushed
+    shows_after = box.host_table.fetch_rows(box.host_table.keys(), create=False)[:, 0].sum()
+    assert shows_before == shows_after
+    with pytest.raises(ValueError):
+        AucRunner(box, [["nope"]], slot_list=["slot0"])
+
+
+def test_cluster_single_process_and_thread_helpers():
+    c = cluster.Cluster.ins()
+    assert c.size() == 1 and c.rank() == 0 and c.nccl_rank(3, 8) == 3
+    assert c.allreduce(5, cluster.OP_MAX) == 5
+    assert np.allclose(c.allreduce_sum([1.0, 2.0]), [1.0, 2.0])
+    c.barrier()
+    hits = [0] * 16
+    cluster.execute_func(16, lambda i: hits.__setitem__(i, i * i))
+    assert hits == [i * i for i in range(16)]
+    acc = np.zeros(1000)
+
+    def fill(b, e):
+        acc[b:e] += 1
+    cluster.exec_range_func(1000, fill, parts=7)
+    assert (acc == 1).all()
+    tc, rc = cluster.get_train_cores(), cluster.get_readins_cores()
+    assert tc and rc
+    assert cluster.set_cpu_affinity(tc + rc) in (True, False)
+
+
+def test_masked_data_norm_matches_definition():
+    torch.manual_seed(0)
+    x = torch.randn(10, 4, requires_grad=True)
+    mask = torch.tensor([1, 0, 1, 1, 0, 1, 1, 1, 0, 1], dtype=torch.bool)
+    bsize, bsum, bsq = torch.full((4,), 100.0), torch.randn(4) * 10, torch.full((4,), 400.0)
+    got = {}
+    y = F.masked_data_norm(x, mask, bsize, bsum, bsq, 1e-4, lambda a, b, c: got.update(size=a, sum=b, sq=c))
+    mean, scale = bsum / bsize, torch.sqrt(bsize / bsq)
+    exp = (x.detach() - mean) * scale
+    exp[~mask] = 0
+    assert torch.allclose(y, exp, atol=1e-6)
+    y.sum().backward()
+    gexp = scale.expand(10, 4).clone()
+    gexp[~mask] = 0
+    assert torch.allclose(x.grad, gexp)
+    xs = x.detach()[mask]
+    assert torch.allclose(got["size"], torch.ones(4))
+    assert torch.allclose(got["sum"], xs.mean(0), atol=1e-6)
+    assert torch.allclose(got["sq"], ((xs - mean) ** 2).mean(0) + 1e-4, atol=1e-5)
+    # no selected row: all three summaries are zero
+    F.masked_data_norm(x, torch.zeros(10, dtype=torch.bool), bsize, bsum, bsq, 1e-4,
+                       lambda a, b, c: got.update(size=a)).sum().backward()
+    assert float(got["size"].sum()) == 0.0
+
+
+def test_store_q_value_and_gpups_names(box):
+    from paddlebox_b200 import ps_gpu
+    q = [torch.rand(4, 1), torch.rand(4, 1)]
+
+    class B:
+        pass
+    b = B()
+    host = F.store_q_value(q, batch=b, device_id=0)
+    assert len(host) == 2 and torch.equal(b.q_values[1], q[1]) and F.stored_q_values(0) is host
+    assert ps_gpu.PSGPUWrapper.get_instance() is box          # one PS per process
+    assert ps_gpu.PSGPUTrainer is CTRTrainer and callable(ps_gpu.pull_gpups_sparse)
+
+
+def test_merge_multi_models(tmp_path, box):
+    keys = np.arange(1, 21, dtype=np.uint64)
+    rows = box.host_table.fetch_rows(keys, create=True).copy()
+    rows[:, 0], rows[:, 1], rows[:, 2] = 10.0, 2.0, 0.5
+    box.host_table.store_rows(keys, rows)
+    box.host_table.save(str(tmp_path / "m1"))
+    rows[:, 0], rows[:, 1], rows[:, 2] = 4.0, 1.0, -0.25
+    box.host_table.store_rows(keys[:10], rows[:10])
+    box.host_table.save(str(tmp_path / "m2"))
+    box.host_table.clear()
+    box.merge_multi_models([str(tmp_path / "m1"), str(tmp_path / "m2")], update_type=0)
+    r = box.host_table.fetch_rows(keys, create=False)
+    assert np.allclose(r[:10, 0], 4.0) and np.allclose(r[:10, 2], -0.25) and np.allclose(r[10:, 0], 10.0)
+    box.host_table.clear()
+    box.merge_multi_models([str(tmp_path / "m1"), str(tmp_path / "m2")], update_type=1)
+    r = box.host_table.fetch_rows(keys, create=False)
+    assert np.allclose(r[:10, 0], 14.0) and np.allclose(r[:10, 1], 3.0) and np.allclose(r[:10, 2], -0.25)

@@ -101,7 +101,7 @@ def test_other_model_families_step_on_cpu(tmp_path, box, cls, kw):
     for _ in range(6):
         ds.prepare_train(1, 0, shuffle=False)
         for batch in ds.batches():
-            losses.append(float(trainer.train_step(batch)))
+            losses.append(float(trainer.train_step(batch).detach()))
     ds.end_pass()
     assert all(np.isfinite(losses)) and np.mean(losses[-2:]) < np.mean(losses[:2])
 
