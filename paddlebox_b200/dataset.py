@@ -17,6 +17,7 @@ batch is packed by a background thread while the current one trains.
 from __future__ import annotations
 
 import ctypes as C
+import os
 import threading
 import queue
 from dataclasses import dataclass, field
@@ -246,9 +247,24 @@ class InMemoryDataset(DatasetBase):
     def local_shuffle(self):
         self._native.local_shuffle(self._shuffle_seed)
 
-    def global_shuffle(self, fleet=None, thread_num: int = 12):
-        """Single-node scope: a global shuffle is a local one; with several nodes records are
-        re-partitioned by ``parallel.shuffle.global_shuffle_records``."""
+    def set_shuffle_dir(self, path: str):
+        """Directory every rank can reach, used to exchange records in ``global_shuffle``."""
+        self._shuffle_dir = path
+
+    def global_shuffle(self, fleet=None, thread_num: int = 12, mode: str | None = None):
+        """Re-partition the loaded records over all ranks (``ShuffleData``, data_set.cc:2422-2604),
+        then shuffle locally.  One process: a local shuffle.  ``mode``: ``random`` (default),
+        ``search_id`` (``FLAGS_enable_shuffle_by_searchid``) or ``ins_id``."""
+        import torch.distributed as dist
+        if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1:
+            import tempfile
+            from .parallel.shuffle import global_shuffle_records
+            if mode is None:
+                mode = "search_id" if FLAGS.enable_shuffle_by_searchid else "random"
+            work = getattr(self, "_shuffle_dir", None) or os.path.join(tempfile.gettempdir(), "pbx_global_shuffle")
+            self._shuffle_round = getattr(self, "_shuffle_round", 0) + 1
+            global_shuffle_records(self, work, mode=mode, seed=self._shuffle_seed,
+                                   tag=f"shuffle{self._shuffle_round}")
         self._native.local_shuffle(self._shuffle_seed)
 
     def slots_shuffle(self, slots: Sequence[str]):

@@ -201,3 +201,36 @@ def gpu_deepfm_data_parallel(rank, world):
     assert all(torch.equal(gathered[0], t) for t in gathered)
     box.end_pass()
     return (losses[0], losses[-1], bool(int(flag)), l2[-1])
+
+
+def cpu_global_shuffle_and_cluster(rank, world):
+    """Each rank loads its own files, the records are re-partitioned over the ranks by
+    search_id, and the host-side Cluster collectives agree."""
+    import tempfile
+    from paddlebox_b200.dataset import DatasetFactory
+    from paddlebox_b200.parallel.cluster import Cluster, OP_MAX, OP_SUM
+    from tests.util_data import slot_vars, write_files
+    base = os.path.join(tempfile.gettempdir(), f"pbx_gs_{os.environ['MASTER_PORT']}")
+    os.makedirs(os.path.join(base, f"r{rank}"), exist_ok=True)
+    ds = DatasetFactory().create_dataset("InMemoryDataset")
+    ds.set_use_var(slot_vars(4, 2))
+    ds.set_batch_size(16)
+    ds.set_thread(1)
+    ds.set_parse_logkey(True)
+    files = write_files(os.path.join(base, f"r{rank}"), n_files=1, lines_per_file=100 + 40 * rank, n_sparse=4,
+                        n_dense=2, key_space=50, seed=rank, logkey=True)
+    ds.set_filelist(files)
+    ds.load_into_memory()
+    n_before = ds.get_memory_data_size()
+    ds.set_shuffle_dir(os.path.join(base, "x"))
+    ds.global_shuffle(mode="search_id")
+    n_after = ds.get_memory_data_size()
+    c = Cluster.ins()
+    total_before = c.allreduce(int(n_before), OP_SUM)
+    total_after = c.allreduce(int(n_after), OP_SUM)
+    biggest = c.allreduce(int(n_after), OP_MAX)
+    sums = c.allreduce_sum([float(rank + 1), 1.0])
+    ranks = c.allgather_object(rank)
+    c.barrier()
+    return dict(before=n_before, after=n_after, total_before=total_before, total_after=total_after,
+                biggest=biggest, sums=sums.tolist(), ranks=ranks)

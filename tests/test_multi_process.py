@@ -47,6 +47,15 @@ def test_two_ranks_gloo_cpu():
     assert abs(outs[0] - outs[1]) < 1e-12 and 0.6 < outs[0] < 0.95     # same global AUC on both ranks
 
 
+def test_global_shuffle_and_cluster_two_ranks_gloo():
+    outs = _spawn(W.cpu_global_shuffle_and_cluster, 2, "gloo")
+    assert outs[0]["before"] == 100 and outs[1]["before"] == 140
+    assert outs[0]["total_before"] == outs[0]["total_after"] == 240          # nothing lost, nothing duplicated
+    assert outs[0]["after"] + outs[1]["after"] == 240 and outs[0]["after"] != 100   # records really moved
+    assert outs[0]["biggest"] == max(outs[0]["after"], outs[1]["after"])
+    assert outs[0]["sums"] == [3.0, 2.0] and outs[1]["ranks"] == [0, 1]
+
+
 def _ngpu():
     return torch.cuda.device_count() if torch.cuda.is_available() else 0
 
