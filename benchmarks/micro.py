@@ -73,6 +73,21 @@ def bench_gemm(out, flush):
                     "tflops": round(fl / us / 1e6, 1), "frac_of_peak": round(fl / us / 1e6 / tf, 3),
                     "cublas_us": round(us_lib, 2), "vs_cublas": round(us_lib / us, 2), "peak_src": src})
         print(out[-1], flush=True)
+        if M * K < (1 << 26):
+            # in-kernel timeline of CTA (0,0,0), cold caches (debug stamps; not a timing of record)
+            lib = N.cuda()
+            N.check(lib.pbx_gemm_debug_enable(1))
+            flush.zero_()
+            fn()
+            ts = (C.c_uint64 * 8)()
+            N.check(lib.pbx_gemm_debug_ts(ts))
+            N.check(lib.pbx_gemm_debug_enable(0))
+            t = [int(x) for x in ts]
+            names = ["setup", "first stage landed", "mainloop issue", "accumulator complete", "epilogue regs->smem",
+                     "stores issued", "exit"]
+            tl = {n: round((t[i + 1] - t[i]) / 1e3, 2) for i, n in enumerate(names)}
+            out.append({"kernel": "gemm_timeline_us", "case": name, **tl})
+            print(out[-1], flush=True)
 
 
 def bench_sparse(out, flush, keys_per_gpu=125_000_000, dim=16, B=4096, S=26, max_bag=5):

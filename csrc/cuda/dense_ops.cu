@@ -7,6 +7,8 @@
 // sigmoid / scale kernels.
 #include "common.cuh"
 
+#define PBX_CT_MAX 12
+
 namespace {
 
 // fp32 [M, K] (ld) -> bf16 [M, ldo] (+ optional bf16 transposed [K, ldt]); 32x32 smem tiles
@@ -14,6 +16,43 @@ __global__ void k_cast_transpose(const float* __restrict__ x, int ld, int M, int
                                  int ldo, __nv_bfloat16* __restrict__ out_t, int ldt) {
   __shared__ float tile[32][33];
   const int m0 = blockIdx.y * 32, k0 = blockIdx.x * 32;
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    int m = m0 + r, k = k0 + threadIdx.x;
+    float v = (m < M && k < K) ? x[(int64_t)m * ld + k] : 0.f;
+    tile[r][threadIdx.x] = v;
+    if (out && m < M && k < K) out[(int64_t)m * ldo + k] = __float2bfloat16(v);
+  }
+  if (!out_t) return;
+  __syncthreads();
+  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
+    int k = k0 + r, m = m0 + threadIdx.x;
+    if (k < K && m < M) out_t[(int64_t)k * ldt + m] = __float2bfloat16(tile[threadIdx.x][r]);
+  }
+}
+
+// The same for up to PBX_CT_MAX tensors in ONE launch (all weights of a tower + its input): a
+// training step is launch-bound (~1.7 us per dependent launch on B200), so five 4-us kernels
+// cost more in gaps than in work.
+struct CastTransposeBatch {
+  int n;
+  int tile_end[PBX_CT_MAX];        // exclusive prefix of 32x32 tiles
+  const float* x[PBX_CT_MAX];
+  __nv_bfloat16* out[PBX_CT_MAX];
+  __nv_bfloat16* out_t[PBX_CT_MAX];
+  int ld[PBX_CT_MAX], M[PBX_CT_MAX], K[PBX_CT_MAX], ldo[PBX_CT_MAX], ldt[PBX_CT_MAX];
+};
+
+__global__ void k_cast_transpose_multi(const __grid_constant__ CastTransposeBatch b) {
+  __shared__ float tile[32][33];
+  int t = 0;
+  while (t < b.n - 1 && (int)blockIdx.x >= b.tile_end[t]) ++t;
+  const int local = blockIdx.x - (t ? b.tile_end[t - 1] : 0);
+  const int M = b.M[t], K = b.K[t], ld = b.ld[t], ldo = b.ldo[t], ldt = b.ldt[t];
+  const int tk = (K + 31) / 32;
+  const int m0 = (local / tk) * 32, k0 = (local % tk) * 32;
+  const float* __restrict__ x = b.x[t];
+  __nv_bfloat16* __restrict__ out = b.out[t];
+  __nv_bfloat16* __restrict__ out_t = b.out_t[t];
   for (int r = threadIdx.y; r < 32; r += blockDim.y) {
     int m = m0 + r, k = k0 + threadIdx.x;
     float v = (m < M && k < K) ? x[(int64_t)m * ld + k] : 0.f;
@@ -52,8 +91,10 @@ __global__ void k_colsum_bf16(const __nv_bfloat16* __restrict__ x, int ld, int M
 // step_dev[0] holds the step count t (float), advanced by the kernel's first thread.
 __global__ void k_adam_flat(float* __restrict__ p, float* __restrict__ g, float* __restrict__ m,
                             float* __restrict__ v, int64_t n, float lr, float b1, float b2, float eps,
-                            float weight_decay, float grad_scale, const float* __restrict__ step_dev,
+                            float weight_decay, float grad_scale, float* __restrict__ step_dev,
                             int zero_grad) {
+  // step_dev[0] = step count, step_dev[1] = blocks finished (as float bits are avoided: counts
+  // stay far below 2^24).  The last block to finish advances the step: every block has read it.
   const float t = step_dev[0] + 1.f;
   const float c1 = 1.f - powf(b1, t), c2 = 1.f - powf(b2, t);
   const float step_size = lr * sqrtf(c2) / c1;
@@ -68,8 +109,16 @@ __global__ void k_adam_flat(float* __restrict__ p, float* __restrict__ g, float*
     p[i] = pi - step_size * mi / (sqrtf(vi) + eps * sqrtf(c2));
     if (zero_grad) g[i] = 0.f;
   }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const float done = atomicAdd(step_dev + 1, 1.f);
+    if (done == (float)(gridDim.x - 1)) {
+      step_dev[1] = 0.f;
+      step_dev[0] = t;
+    }
+  }
 }
-__global__ void k_step_inc(float* step_dev) { step_dev[0] += 1.f; }
 
 __global__ void k_sgd_flat(float* __restrict__ p, float* __restrict__ g, int64_t n, float lr, float grad_scale,
                            int zero_grad) {
@@ -95,6 +144,46 @@ __global__ void k_sigmoid_logloss(const float* __restrict__ logit, const float* 
   }
   for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
   if ((threadIdx.x & 31) == 0 && loss_sum) atomicAdd(loss_sum, local / (float)B);
+}
+
+// CTR head in one pass: logit = tower + extra + bias; pred = sigmoid(logit); mean log-loss;
+// dlogit = (pred - label) / B kept for the backward.  Replaces three adds, a copy and the loss op.
+__global__ void k_ctr_head_fwd(const float* __restrict__ tower, int ld_tower, const float* __restrict__ extra,
+                               const float* __restrict__ bias, const float* __restrict__ label, int ld_label, int B,
+                               float* __restrict__ pred, float* __restrict__ loss_sum,
+                               float* __restrict__ dlogit) {
+  float local = 0.f;
+  const float bv = bias ? bias[0] : 0.f;
+  const float invB = 1.f / (float)B;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < B; i += gridDim.x * blockDim.x) {
+    float z = tower[(int64_t)i * ld_tower] + bv;
+    if (extra) z += extra[i];
+    const float y = label[(int64_t)i * ld_label];
+    const float p = 1.f / (1.f + __expf(-z));
+    pred[i] = p;
+    local += fmaxf(z, 0.f) - z * y + log1pf(__expf(-fabsf(z)));
+    dlogit[i] = (p - y) * invB;
+  }
+  for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+  if ((threadIdx.x & 31) == 0) atomicAdd(loss_sum, local * invB);
+}
+
+// backward of the head: every logit term receives gloss * dlogit; the bias its sum.
+__global__ void k_ctr_head_bwd(const float* __restrict__ dlogit, const float* __restrict__ gloss, int B,
+                               float* __restrict__ d_tower, float* __restrict__ d_extra,
+                               float* __restrict__ d_bias) {
+  const float g = gloss[0];
+  float local = 0.f;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < B; i += gridDim.x * blockDim.x) {
+    const float d = dlogit[i] * g;
+    if (d_tower) d_tower[i] = d;
+    if (d_extra) d_extra[i] = d;
+    local += d;
+  }
+  if (d_bias) {
+    for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+    if ((threadIdx.x & 31) == 0) atomicAdd(d_bias, local);
+  }
 }
 
 // DeepFM first/second-order head on pooled slot embeddings.
@@ -290,6 +379,43 @@ int pbx_cast_transpose(const float* x, int ld, int M, int K, void* out_bf16, int
   return 0;
 }
 
+// n <= PBX_CT_MAX tensors; arrays of length n (out / out_t entries may be null)
+int pbx_cast_transpose_multi(int n, const float* const* x, const int* ld, const int* M, const int* K,
+                             void* const* out, const int* ldo, void* const* out_t, const int* ldt, cudaStream_t st) {
+  PBX_REQUIRE(n >= 1 && n <= PBX_CT_MAX, "cast_transpose_multi: %d tensors (max %d)", n, PBX_CT_MAX);
+  CastTransposeBatch b;
+  memset(&b, 0, sizeof(b));
+  b.n = n;
+  int tiles = 0;
+  for (int i = 0; i < n; ++i) {
+    PBX_REQUIRE(M[i] > 0 && K[i] > 0, "cast_transpose_multi: empty tensor %d", i);
+    tiles += ((M[i] + 31) / 32) * ((K[i] + 31) / 32);
+    b.tile_end[i] = tiles;
+    b.x[i] = x[i]; b.out[i] = (__nv_bfloat16*)out[i]; b.out_t[i] = (__nv_bfloat16*)out_t[i];
+    b.ld[i] = ld[i]; b.M[i] = M[i]; b.K[i] = K[i]; b.ldo[i] = ldo[i]; b.ldt[i] = ldt[i];
+  }
+  k_cast_transpose_multi<<<tiles, dim3(32, 8), 0, st>>>(b);
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
+  return 0;
+}
+
+int pbx_ctr_head_fwd(const float* tower, int ld_tower, const float* extra, const float* bias, const float* label,
+                     int ld_label, int B, float* pred, float* loss_sum, float* dlogit, cudaStream_t st) {
+  if (B <= 0) return 0;
+  k_ctr_head_fwd<<<pbx_grid_for(B, 256, 1), 256, 0, st>>>(tower, ld_tower, extra, bias, label, ld_label, B, pred,
+                                                          loss_sum, dlogit);
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
+  return 0;
+}
+
+int pbx_ctr_head_bwd(const float* dlogit, const float* gloss, int B, float* d_tower, float* d_extra, float* d_bias,
+                     cudaStream_t st) {
+  if (B <= 0) return 0;
+  k_ctr_head_bwd<<<pbx_grid_for(B, 256, 1), 256, 0, st>>>(dlogit, gloss, B, d_tower, d_extra, d_bias);
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
+  return 0;
+}
+
 int pbx_colsum_bf16(const void* x, int ld, int M, int N, float* out, cudaStream_t st) {
   if (M <= 0 || N <= 0) return 0;
   int gy = (M + 63) / 64;   // 64 rows per block: short serial loops, plenty of blocks
@@ -304,7 +430,6 @@ int pbx_adam_flat(float* p, float* g, float* m, float* v, int64_t n, float lr, f
   if (n <= 0) return 0;
   k_adam_flat<<<pbx_grid_for(n, 256, 8), 256, 0, st>>>(p, g, m, v, n, lr, b1, b2, eps, weight_decay, grad_scale,
                                                        step_dev, zero_grad);
-  k_step_inc<<<1, 1, 0, st>>>(step_dev);
   PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }

@@ -23,8 +23,8 @@ namespace {
 
 constexpr int BM = 128;
 constexpr int BK = 64;  // 64 bf16 = 128 bytes = one swizzle row
-constexpr int STAGES = 4;
-constexpr int GEMM_THREADS = 192;  // 6 warps
+constexpr int GEMM_THREADS = 320;  // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue
+constexpr int EPI_THREADS = 256;
 
 struct GemmEpilogue {
   const float* bias;          // [N] or null
@@ -38,7 +38,9 @@ struct GemmEpilogue {
   float alpha;
   float* col_out;             // optional: output column `col_split` goes to col_out[row] instead of
   int col_split;              // out_f32 (bias gradient from a ones row appended to the B operand)
+  unsigned long long* ts;     // optional debug timeline of CTA (0,0,0): 8 globaltimer stamps
 };
+#define GEMM_TS(i) do { if (ep.ts && (blockIdx.x | blockIdx.y | blockIdx.z) == 0) ep.ts[i] = pbx_globaltimer(); } while (0)
 
 // ---------------- PTX wrappers ----------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -133,9 +135,13 @@ struct SmemLayout {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int TOTAL = STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+  // deep pipelines: the MLP-tower GEMMs have 4-8 k-blocks and start cold, so every k-block that
+  // is in flight at once removes one exposed DRAM round trip from the main loop
+  static constexpr int STAGES = (196 * 1024 / STAGE_BYTES) > 8 ? 8 : (196 * 1024 / STAGE_BYTES);
+  static constexpr int BAR_BYTES = 256;
+  static constexpr int TOTAL = STAGES * STAGE_BYTES + 1024 /*align slack*/ + BAR_BYTES + BN * 4 /*bias*/;
   // the epilogue reuses the stage memory for a row-major and a transposed bf16 staging tile
-  static_assert(BM * (BN + 8) * 2 + BN * (BM + 8) * 2 <= STAGES * STAGE_BYTES, "staging tiles do not fit");
+  static_assert(BM * (BN + 8) * 2 + BN * (BM + 32) * 2 <= STAGES * STAGE_BYTES, "staging tiles do not fit");
 };
 
 template <int BN>
@@ -145,7 +151,9 @@ k_gemm_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
   extern __shared__ uint8_t smem_raw[];
   using L = SmemLayout<BN>;
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  constexpr int STAGES = L::STAGES;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * L::STAGE_BYTES);
+  float* s_bias = reinterpret_cast<float*>(smem + STAGES * L::STAGE_BYTES + L::BAR_BYTES);
   uint64_t* empty_bar = full_bar + STAGES;
   uint64_t* tmem_full_bar = empty_bar + STAGES;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full_bar + 1);
@@ -158,6 +166,7 @@ k_gemm_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
   const int kb_begin = blockIdx.z * kb_per_split;
   const int kb_end = min(kb_begin + kb_per_split, num_kb_total);
   const int num_kb = kb_end - kb_begin;
+  if (threadIdx.x == 0) GEMM_TS(0);
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
@@ -174,6 +183,7 @@ k_gemm_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) GEMM_TS(1);
 
   if (num_kb > 0) {
     if (warp == 0) {
@@ -200,6 +210,7 @@ k_gemm_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
           const uint32_t ph = (uint32_t)(i / STAGES) & 1u;
           mbar_wait(full_bar + s, ph);
           tc_fence_after();
+          if (i == 0) GEMM_TS(2);
           uint8_t* sa = smem + s * L::STAGE_BYTES;
           uint8_t* sb = sa + L::A_BYTES;
           const uint64_t da = make_smem_desc(sa);
@@ -212,10 +223,13 @@ k_gemm_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
           umma_commit(empty_bar + s);  // frees the smem stage when these MMAs retire
         }
         umma_commit(tmem_full_bar);    // accumulator complete
+        GEMM_TS(3);
       }
       __syncwarp();
     } else {
-      // ===== epilogue: warps 2..5, TMEM lane quadrant = warp % 4 =====
+      // ===== epilogue: warps 2..9.  TMEM lane quadrant = warp % 4 (hardware rule); the two warps
+      // of a quadrant split the tile's columns in halves.  One warp per scheduler is latency-bound
+      // (the in-kernel timeline showed the 4-warp epilogue at 2x the main loop), hence eight. =====
       // bf16 outputs are staged through shared memory (the pipeline stages are free once the
       // accumulator is complete) so that both the row-major tile and its transpose leave the SM
       // as 16-byte, fully coalesced stores.  (Writing the transpose straight from registers
@@ -224,50 +238,74 @@ k_gemm_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
       const int q = warp & 3;
       const int rl = q * 32 + lane;          // row inside the tile
       const int row = m0 + rl;
-      constexpr int LDC = BN + 8, LDT = BM + 8;
+      const int half = (warp - 2) >> 2;      // which half of the columns
+      constexpr int NCH = BN >= 64 ? BN / 64 : 1;            // 32-column chunks per warp
+      const bool active = BN >= 64 || half == 0;
+      constexpr int LDC = BN + 8, LDT = BM + 32;             // LDT/2 = 16 (mod 32): paired-row stores of
+                                                             // neighbouring columns hit disjoint banks
       __nv_bfloat16* sC = reinterpret_cast<__nv_bfloat16*>(smem);
       __nv_bfloat16* sT = sC + BM * LDC;
       const bool stage = ep.out_bf16 != nullptr || ep.out_t != nullptr;
+      const int et = threadIdx.x - 64;       // 0..255 over the eight epilogue warps
+      // While the main loop runs these warps are idle: fetch everything the epilogue reads from
+      // global memory NOW (bias -> shared, ReLU mask of this thread's row -> registers), so no
+      // cold DRAM round trip sits between the accumulator and the stores.
+      if (ep.bias)
+        for (int i = et; i < BN; i += EPI_THREADS) s_bias[i] = (n0 + i < N) ? __ldg(ep.bias + n0 + i) : 0.f;
+      constexpr bool kMaskRegs = BN <= 128;
+      uint4 mk[kMaskRegs ? NCH * 4 : 1];
+      const int cbase = BN >= 64 ? half * (BN / 2) : 0;
+      const bool mask_pre = kMaskRegs && ep.mask && row < M && n0 + BN <= N && (ep.ld_mask & 7) == 0 &&
+                            ((uintptr_t)ep.mask & 15) == 0 && (n0 & 7) == 0;
+      if (kMaskRegs && mask_pre) {
+        const uint4* mrow4 = reinterpret_cast<const uint4*>(ep.mask + (int64_t)row * ep.ld_mask + n0 + cbase);
+#pragma unroll
+        for (int j = 0; j < NCH * 4; ++j) mk[j] = __ldg(mrow4 + j);
+      }
+      asm volatile("bar.sync 1, 256;" ::: "memory");   // s_bias visible to the eight epilogue warps
       mbar_wait(tmem_full_bar, 0);
       tc_fence_after();
-#pragma unroll 1
-      for (int c0 = 0; c0 < BN; c0 += 32) {
+      if (threadIdx.x == 64) GEMM_TS(4);
+#pragma unroll
+      for (int cc = 0; cc < NCH; ++cc) {
+        const int c0 = cbase + cc * 32;
+        if (!active) break;
         uint32_t r[32];
         tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
         if (n0 + c0 >= N) continue;
         float v[32];
-        if (ep.bias && n0 + c0 + 32 <= N && ((n0 + c0) & 3) == 0 && ((uintptr_t)ep.bias & 15) == 0) {
-          // the 32 bias values of this chunk as 8 independent 16-byte (warp-uniform) loads
-          float4 bq[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) bq[j] = __ldg(reinterpret_cast<const float4*>(ep.bias + n0 + c0) + j);
+        if (ep.bias) {
 #pragma unroll
           for (int j = 0; j < 8; ++j) {
-            v[4 * j] = __uint_as_float(r[4 * j]) * ep.alpha + bq[j].x;
-            v[4 * j + 1] = __uint_as_float(r[4 * j + 1]) * ep.alpha + bq[j].y;
-            v[4 * j + 2] = __uint_as_float(r[4 * j + 2]) * ep.alpha + bq[j].z;
-            v[4 * j + 3] = __uint_as_float(r[4 * j + 3]) * ep.alpha + bq[j].w;
+            const float4 bq = *reinterpret_cast<const float4*>(s_bias + c0 + 4 * j);   // warp-uniform: broadcast
+            v[4 * j] = __uint_as_float(r[4 * j]) * ep.alpha + bq.x;
+            v[4 * j + 1] = __uint_as_float(r[4 * j + 1]) * ep.alpha + bq.y;
+            v[4 * j + 2] = __uint_as_float(r[4 * j + 2]) * ep.alpha + bq.z;
+            v[4 * j + 3] = __uint_as_float(r[4 * j + 3]) * ep.alpha + bq.w;
           }
         } else {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) {
-            float x = __uint_as_float(r[j]) * ep.alpha;
-            const int n = n0 + c0 + j;
-            if (ep.bias && n < N) x += __ldg(ep.bias + n);
-            v[j] = x;
-          }
+          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]) * ep.alpha;
         }
         if (ep.relu) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) v[j] = fmaxf(v[j], 0.f);
         }
-        if (ep.mask && row < M) {
+        if (kMaskRegs && mask_pre) {
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const __nv_bfloat16* mb = reinterpret_cast<const __nv_bfloat16*>(&mk[kMaskRegs ? cc * 4 + j : 0]);
+#pragma unroll
+            for (int e = 0; e < 8; ++e)
+              if (!(__bfloat162float(mb[e]) > 0.f)) v[8 * j + e] = 0.f;
+          }
+        } else if (ep.mask && row < M) {
           const __nv_bfloat16* mrow = ep.mask + (int64_t)row * ep.ld_mask + n0 + c0;
           if (n0 + c0 + 32 <= N && (ep.ld_mask & 7) == 0) {
 #pragma unroll
             for (int j = 0; j < 32; j += 8) {
-              const uint4 mk = __ldg(reinterpret_cast<const uint4*>(mrow + j));
-              const __nv_bfloat16* mb = reinterpret_cast<const __nv_bfloat16*>(&mk);
+              const uint4 mq = __ldg(reinterpret_cast<const uint4*>(mrow + j));
+              const __nv_bfloat16* mb = reinterpret_cast<const __nv_bfloat16*>(&mq);
 #pragma unroll
               for (int e = 0; e < 8; ++e)
                 if (!(__bfloat162float(mb[e]) > 0.f)) v[j + e] = 0.f;
@@ -294,8 +332,17 @@ k_gemm_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
             }
           }
           if (ep.out_t) {
+            // neighbouring lanes (rows rl, rl^1) swap one column of each column pair, so every lane
+            // writes one packed (row, row+1) bf16x2 instead of two 2-byte stores
+            const bool odd = lane & 1;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) sT[(c0 + j) * LDT + rl] = __float2bfloat16(v[j]);
+            for (int j = 0; j < 32; j += 2) {
+              const float mine = odd ? v[j + 1] : v[j];
+              const float give = odd ? v[j] : v[j + 1];
+              const float got = __shfl_xor_sync(0xffffffffu, give, 1);
+              const __nv_bfloat162 pr = odd ? __floats2bfloat162_rn(got, mine) : __floats2bfloat162_rn(mine, got);
+              *reinterpret_cast<__nv_bfloat162*>(sT + (c0 + j + (odd ? 1 : 0)) * LDT + (rl & ~1)) = pr;
+            }
           }
         }
         if (ep.out_f32 && row < M) {
@@ -328,47 +375,67 @@ k_gemm_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
           }
         }
       }
+      if (threadIdx.x == 64) GEMM_TS(5);
       if (stage) {
-        asm volatile("bar.sync 1, 128;" ::: "memory");   // the four epilogue warps only
-        const int et = threadIdx.x - 64;
+        asm volatile("bar.sync 1, 256;" ::: "memory");   // the eight epilogue warps only
         if (ep.out_bf16) {
           constexpr int VPR = BN / 8;
-          for (int idx = et; idx < BM * VPR; idx += 128) {
-            const int r_ = idx / VPR, cv = idx % VPR;
-            const int gr = m0 + r_, gc = n0 + cv * 8;
-            if (gr >= M || gc >= N) continue;
-            const uint4 val = *reinterpret_cast<const uint4*>(sC + r_ * LDC + cv * 8);
-            __nv_bfloat16* o = ep.out_bf16 + (int64_t)gr * ep.ld_out + gc;
-            if (gc + 8 <= N && (ep.ld_out & 7) == 0) {
-              *reinterpret_cast<uint4*>(o) = val;
-            } else {
-              const __nv_bfloat16* e8 = reinterpret_cast<const __nv_bfloat16*>(&val);
-              for (int e = 0; e < 8 && gc + e < N; ++e) o[e] = e8[e];
+          const bool vec_ok = (ep.ld_out & 7) == 0;
+          for (int base = 0; base < BM * VPR; base += EPI_THREADS * 4) {   // 4 independent 16-byte moves per thread
+            uint4 val[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int idx = base + u * EPI_THREADS + et;
+              if (idx < BM * VPR) val[u] = *reinterpret_cast<const uint4*>(sC + (idx / VPR) * LDC + (idx % VPR) * 8);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int idx = base + u * EPI_THREADS + et;
+              const int gr = m0 + idx / VPR, gc = n0 + (idx % VPR) * 8;
+              if (idx >= BM * VPR || gr >= M || gc >= N) continue;
+              __nv_bfloat16* o = ep.out_bf16 + (int64_t)gr * ep.ld_out + gc;
+              if (gc + 8 <= N && vec_ok) {
+                *reinterpret_cast<uint4*>(o) = val[u];
+              } else {
+                const __nv_bfloat16* e8 = reinterpret_cast<const __nv_bfloat16*>(&val[u]);
+                for (int e = 0; e < 8 && gc + e < N; ++e) o[e] = e8[e];
+              }
             }
           }
         }
         if (ep.out_t) {
           constexpr int VPR = BM / 8;
-          for (int idx = et; idx < BN * VPR; idx += 128) {
-            const int n_ = idx / VPR, mv = idx % VPR;
-            const int gn = n0 + n_, gm = m0 + mv * 8;
-            if (gn >= N || gm >= M) continue;
-            const uint4 val = *reinterpret_cast<const uint4*>(sT + n_ * LDT + mv * 8);
-            __nv_bfloat16* o = ep.out_t + (int64_t)gn * ep.ld_t + gm;
-            if (gm + 8 <= M && (ep.ld_t & 7) == 0) {
-              *reinterpret_cast<uint4*>(o) = val;
-            } else {
-              const __nv_bfloat16* e8 = reinterpret_cast<const __nv_bfloat16*>(&val);
-              for (int e = 0; e < 8 && gm + e < M; ++e) o[e] = e8[e];
+          const bool vec_ok = (ep.ld_t & 7) == 0;
+          for (int base = 0; base < BN * VPR; base += EPI_THREADS * 4) {
+            uint4 val[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int idx = base + u * EPI_THREADS + et;
+              if (idx < BN * VPR) val[u] = *reinterpret_cast<const uint4*>(sT + (idx / VPR) * LDT + (idx % VPR) * 8);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+              const int idx = base + u * EPI_THREADS + et;
+              const int gn = n0 + idx / VPR, gm = m0 + (idx % VPR) * 8;
+              if (idx >= BN * VPR || gn >= N || gm >= M) continue;
+              __nv_bfloat16* o = ep.out_t + (int64_t)gn * ep.ld_t + gm;
+              if (gm + 8 <= M && vec_ok) {
+                *reinterpret_cast<uint4*>(o) = val[u];
+              } else {
+                const __nv_bfloat16* e8 = reinterpret_cast<const __nv_bfloat16*>(&val[u]);
+                for (int e = 0; e < 8 && gm + e < M; ++e) o[e] = e8[e];
+              }
             }
           }
         }
       }
     }
   }
+  if (threadIdx.x == 64) GEMM_TS(6);
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, BN);
+  if (threadIdx.x == 0) GEMM_TS(7);
 }
 
 // --------- plain SIMT kernel with the same contract: numerics cross-check / fallback ---------
@@ -453,9 +520,31 @@ int launch_tc(const __nv_bfloat16* A, int lda, const __nv_bfloat16* B, int ldb, 
   return 0;
 }
 
+unsigned long long* g_gemm_ts = nullptr;   // device buffer of 8 stamps when the debug timeline is on
+
 }  // namespace
 
 extern "C" {
+
+// Debug timeline of CTA (0,0,0) of the next tcgen05 GEMM launches: kernel entry, setup done, first
+// stage landed, last MMA issued, accumulator complete, epilogue registers done, stores issued, exit.
+int pbx_gemm_debug_enable(int on) {
+  if (on && !g_gemm_ts) {
+    PBX_CUDA_CHECK(cudaMalloc(&g_gemm_ts, 8 * sizeof(unsigned long long)));
+    PBX_CUDA_CHECK(cudaMemset(g_gemm_ts, 0, 8 * sizeof(unsigned long long)));
+  } else if (!on && g_gemm_ts) {
+    cudaFree(g_gemm_ts);
+    g_gemm_ts = nullptr;
+  }
+  return 0;
+}
+
+int pbx_gemm_debug_ts(unsigned long long* out8) {
+  PBX_REQUIRE(g_gemm_ts != nullptr, "gemm debug timeline is off");
+  PBX_CUDA_CHECK(cudaDeviceSynchronize());
+  PBX_CUDA_CHECK(cudaMemcpy(out8, g_gemm_ts, 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  return 0;
+}
 
 // impl: 0 = tcgen05 (default), 1 = SIMT cross-check.  block_n in {32, 64, 128, 256} (0 = auto).
 // Requirements for the tcgen05 path: A/B 16-byte aligned, lda/ldb multiples of 8 elements.
@@ -477,6 +566,7 @@ int pbx_gemm_bf16_tn(const void* A, int lda, const void* B, int ldb, int M, int 
   ep.alpha = alpha;
   ep.col_out = col_out;
   ep.col_split = col_split;
+  ep.ts = g_gemm_ts;
   if (splitk > 1) PBX_REQUIRE(accumulate && out_f32 && !out_bf16 && !out_t && !relu && !bias && !mask,
                               "gemm: split-K needs a pure fp32 accumulate epilogue");
   if (impl == 1) {

@@ -90,6 +90,9 @@ int pbx_key2slot(const int32_t* d_lod, int B, int S, int64_t n, int32_t* d_out, 
  * C = epilogue(alpha * A[M,K] . B[N,K]^T); A, B bf16 K-contiguous.
  * reference call sites: scaled_fc_op.cu:214, batch_fc_op.cu:243, rank_attention_op.cu:110,
  * phi mul/matmul/fc kernels (all cuBLAS). */
+/* debug: in-kernel timeline (8 globaltimer stamps of CTA 0) of the next tcgen05 GEMM launches */
+int pbx_gemm_debug_enable(int on);
+int pbx_gemm_debug_ts(unsigned long long* out8);
 int pbx_gemm_bf16_tn(const void* A, int lda, const void* B, int ldb, int M, int N, int K, const float* bias,
                      const void* mask, int ld_mask, void* out_bf16, int ld_out, void* out_t, int ld_t,
                      float* out_f32, int ld_f32, int relu, int accumulate, float alpha, int splitk, int block_n,
@@ -100,12 +103,24 @@ int pbx_gemm_bf16_tn(const void* A, int lda, const void* B, int ldb, int M, int 
 /* ---- dense helpers (csrc/cuda/dense_ops.cu) --------------------------------- */
 int pbx_cast_transpose(const float* x, int ld, int M, int K, void* out_bf16, int ldo, void* out_t, int ldt,
                        pbx_stream_t stream);
+/* the same for n <= 12 tensors in one launch (arrays of length n; out / out_t entries may be NULL) */
+int pbx_cast_transpose_multi(int n, const float* const* x, const int* ld, const int* M, const int* K,
+                             void* const* out, const int* ldo, void* const* out_t, const int* ldt,
+                             pbx_stream_t stream);
 int pbx_colsum_bf16(const void* x, int ld, int M, int N, float* out, pbx_stream_t stream);
+/* step_dev: 2 floats {step count, scratch}; the kernel advances the step itself (no second launch) */
 int pbx_adam_flat(float* p, float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
                   float weight_decay, float grad_scale, float* step_dev, int zero_grad, pbx_stream_t stream);
 int pbx_sgd_flat(float* p, float* g, int64_t n, float lr, float grad_scale, int zero_grad, pbx_stream_t stream);
 int pbx_sigmoid_logloss(const float* logit, const float* label, int B, float* pred, float* loss_sum,
                         float* dlogit, float gscale, pbx_stream_t stream);
+/* fused CTR head: logit = tower[i*ld_tower] + extra[i] + bias[0]; pred, mean log-loss (added to
+ * *loss_sum) and dlogit = (pred - label)/B in one pass; the backward scales dlogit by *gloss and
+ * adds its sum to *d_bias.  extra / bias / d_* may be NULL. */
+int pbx_ctr_head_fwd(const float* tower, int ld_tower, const float* extra, const float* bias, const float* label,
+                     int ld_label, int B, float* pred, float* loss_sum, float* dlogit, pbx_stream_t stream);
+int pbx_ctr_head_bwd(const float* dlogit, const float* gloss, int B, float* d_tower, float* d_extra, float* d_bias,
+                     pbx_stream_t stream);
 int pbx_fm_fwd(const float* x, int ldx, int B, int S, int E, int wcol, int vcol, int D, float* fm,
                pbx_stream_t stream);
 int pbx_fm_bwd(const float* x, int ldx, const float* g, int B, int S, int E, int wcol, int vcol, int D, float* dx,

@@ -90,8 +90,7 @@ class CtrDnn(CTRModelBase):
 
     def forward(self, batch: SlotBatch):
         x, _, labels = self.features(batch)
-        logit = self.tower(x).view(-1)
-        loss, pred = F.sigmoid_log_loss(logit, labels[:, 0])
+        loss, pred = F.ctr_head(self.tower(x), labels[:, 0])
         return loss, {"pred": pred, "label": labels[:, 0]}
 
 
@@ -110,8 +109,7 @@ class WideDeep(CTRModelBase):
         wide = pooled[:, 2::E].sum(1)                                   # sum of embed_w over slots
         if self.dense_dim:
             wide = wide + x[:, self.sparse_width:] @ self.wide_dense
-        logit = self.tower(x).view(-1) + wide + self.wide_bias
-        loss, pred = F.sigmoid_log_loss(logit, labels[:, 0])
+        loss, pred = F.ctr_head(self.tower(x), labels[:, 0], extra=wide, bias=self.wide_bias)
         return loss, {"pred": pred, "label": labels[:, 0]}
 
 
@@ -128,8 +126,7 @@ class DeepFM(CTRModelBase):
         E = self.attrs.out_width(self.slot_width)
         fm_in = x if self.data_norm is None else pooled     # x's leading columns are the pooled slots
         fm = F.fm_interaction(fm_in, self.num_slots, E, 2, 3, self.embedx_dim)
-        logit = self.tower(x).view(-1) + fm + self.bias
-        loss, pred = F.sigmoid_log_loss(logit, labels[:, 0])
+        loss, pred = F.ctr_head(self.tower(x), labels[:, 0], extra=fm, bias=self.bias)
         return loss, {"pred": pred, "label": labels[:, 0]}
 
 
@@ -155,8 +152,7 @@ class MMoE(CTRModelBase):
         for t in range(self.num_tasks):
             g = torch.softmax(self.gates[t](x), dim=1)         # [B, E]
             mix = torch.einsum("be,ebh->bh", g, ex)
-            logit = self.towers[t](mix).view(-1)
-            l, p = F.sigmoid_log_loss(logit, labels[:, t])
+            l, p = F.ctr_head(self.towers[t](mix), labels[:, t])
             losses.append(l)
             preds.append(p)
         loss = torch.stack(losses).sum()

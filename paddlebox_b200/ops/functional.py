@@ -189,6 +189,59 @@ def sigmoid_log_loss(logit: torch.Tensor, label: torch.Tensor):
     return _SigmoidLogLoss.apply(logit, label)
 
 
+class _CtrHead(torch.autograd.Function):
+    """logit = tower + extra + bias -> (mean log-loss, pred) as one kernel forward, one backward."""
+
+    @staticmethod
+    def forward(ctx, tower, extra, bias, label):
+        B = tower.shape[0]
+        assert tower.dim() in (1, 2) and (tower.dim() == 1 or tower.shape[1] == 1)
+        dev = tower.device
+        pred = torch.empty(B, dtype=torch.float32, device=dev)
+        loss = torch.zeros((), dtype=torch.float32, device=dev)
+        dlogit = torch.empty(B, dtype=torch.float32, device=dev)
+        if extra is not None:
+            extra = extra.contiguous()
+        assert label.dtype == torch.float32
+        N.check(N.cuda().pbx_ctr_head_fwd(N.ptr(tower), tower.stride(0), N.ptr(extra), N.ptr(bias), N.ptr(label),
+                                          label.stride(0), B, N.ptr(pred), N.ptr(loss), N.ptr(dlogit),
+                                          N.stream_ptr()), "pbx_ctr_head_fwd")
+        ctx.save_for_backward(dlogit)
+        ctx.shape = tuple(tower.shape)
+        ctx.has = (extra is not None, bias is not None)
+        ctx.mark_non_differentiable(pred)
+        return loss, pred
+
+    @staticmethod
+    def backward(ctx, gloss, gpred):
+        (dlogit,) = ctx.saved_tensors
+        B = dlogit.numel()
+        need_t, need_e, need_b = ctx.needs_input_grad[0], ctx.needs_input_grad[1] and ctx.has[0], \
+            ctx.needs_input_grad[2] and ctx.has[1]
+        d_tower = torch.empty(ctx.shape, dtype=torch.float32, device=dlogit.device) if need_t else None
+        d_extra = torch.empty(B, dtype=torch.float32, device=dlogit.device) if need_e else None
+        d_bias = torch.zeros(1, dtype=torch.float32, device=dlogit.device) if need_b else None
+        N.check(N.cuda().pbx_ctr_head_bwd(N.ptr(dlogit), N.ptr(gloss.contiguous()), B, N.ptr(d_tower), N.ptr(d_extra),
+                                          N.ptr(d_bias), N.stream_ptr()), "pbx_ctr_head_bwd")
+        return d_tower, d_extra, d_bias, None
+
+
+def ctr_head(tower: torch.Tensor, label: torch.Tensor, extra: torch.Tensor | None = None,
+             bias: torch.Tensor | None = None):
+    """(mean log-loss, pred) of ``sigmoid(tower + extra + bias)`` against ``label``.
+
+    ``tower`` [B] or [B, 1] (the last tower layer's output), ``extra`` [B] further logit terms
+    (FM / wide part), ``bias`` [1] parameter, ``label`` [B] float32 (may be a strided column)."""
+    if not tower.is_cuda:
+        z = tower.reshape(-1)
+        if extra is not None:
+            z = z + extra
+        if bias is not None:
+            z = z + bias
+        return sigmoid_log_loss(z, label)
+    return _CtrHead.apply(tower, extra, bias, label)
+
+
 # ------------------------------------------------------------------ misc CTR utilities
 def row_gather(table: torch.Tensor, idx: torch.Tensor) -> torch.Tensor:
     """Replica-cache gather ``out[i] = table[idx[i]]`` (pull_cache_value, box_wrapper.cu:1210-1224)."""

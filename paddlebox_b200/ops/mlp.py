@@ -59,6 +59,27 @@ def cast_transpose(x: torch.Tensor, out: torch.Tensor | None, out_t: torch.Tenso
             "pbx_cast_transpose")
 
 
+CT_MAX = 12
+
+
+def cast_transpose_multi(items) -> None:
+    """``items``: (x fp32 [M, K], out bf16 | None, out_t bf16 | None) triples, cast (and transposed)
+    in ONE launch per 12 tensors — a training step is bound by the number of dependent launches."""
+    for i0 in range(0, len(items), CT_MAX):
+        chunk = items[i0:i0 + CT_MAX]
+        n = len(chunk)
+        xs = (C.c_void_p * n)(*[x.data_ptr() for x, _, _ in chunk])
+        outs = (C.c_void_p * n)(*[o.data_ptr() if o is not None else None for _, o, _ in chunk])
+        outts = (C.c_void_p * n)(*[t.data_ptr() if t is not None else None for _, _, t in chunk])
+        ld = (C.c_int * n)(*[x.stride(0) for x, _, _ in chunk])
+        M = (C.c_int * n)(*[x.shape[0] for x, _, _ in chunk])
+        K = (C.c_int * n)(*[x.shape[1] for x, _, _ in chunk])
+        ldo = (C.c_int * n)(*[o.stride(0) if o is not None else 0 for _, o, _ in chunk])
+        ldt = (C.c_int * n)(*[t.stride(0) if t is not None else 0 for _, _, t in chunk])
+        N.check(N.cuda().pbx_cast_transpose_multi(n, xs, ld, M, K, outs, ldo, outts, ldt, N.stream_ptr()),
+                "pbx_cast_transpose_multi")
+
+
 def colsum_bf16(x: torch.Tensor, M: int, Nn: int, out: torch.Tensor) -> None:
     N.check(N.cuda().pbx_colsum_bf16(N.ptr(x), x.stride(0), M, Nn, N.ptr(out), N.stream_ptr()), "pbx_colsum_bf16")
 
@@ -131,9 +152,13 @@ class FusedMLP(nn.Module):
         version tracking (paddlebox_b200 optimizers do)."""
         self._dirty = True
 
-    def _refresh_bf16(self) -> None:
+    def _refresh_bf16(self, extra=None) -> None:
+        """bf16 (+ transposed) copies of the weights when they changed, and of ``extra`` (the
+        tower input triple), all in one launch."""
         vers = tuple(w._version for w in self.weights)
         if not self._dirty and vers == self._versions and self._wb is not None:
+            if extra is not None:
+                cast_transpose_multi([extra])
             return
         dev = self.weights[0].device
         if self._wb is None:
@@ -141,8 +166,10 @@ class FusedMLP(nn.Module):
                         for w in self.weights]
             self._wbt = [torch.zeros(w.shape[1], _pad8(w.shape[0]), dtype=torch.bfloat16, device=dev)
                          for w in self.weights]
-        for w, wb, wbt in zip(self.weights, self._wb, self._wbt):
-            cast_transpose(w.data, wb, wbt)
+        items = [(w.data, wb, wbt) for w, wb, wbt in zip(self.weights, self._wb, self._wbt)]
+        if extra is not None:
+            items.append(extra)
+        cast_transpose_multi(items)
         self._dirty = False
         self._versions = vers
 
@@ -165,8 +192,7 @@ class FusedMLP(nn.Module):
         if ws is None:
             ws = self._ws[B] = _Workspace(self.dims, B, x.device)
         self._cur = ws
-        self._refresh_bf16()
-        cast_transpose(x.contiguous() if x.stride(1) != 1 else x, ws.H[0], ws.Ht[0])
+        self._refresh_bf16((x.contiguous() if x.stride(1) != 1 else x, ws.H[0], ws.Ht[0]))
         L = len(self.weights)
         out = torch.empty(B, self.dims[-1], dtype=torch.float32, device=x.device)
         for l in range(L):

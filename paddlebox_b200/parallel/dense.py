@@ -67,7 +67,7 @@ class DenseParamStore:
             p.grad = self.gflat[o:o + n].view_as(p)
         self.m = torch.zeros_like(self.flat) if with_moments else None
         self.v = torch.zeros_like(self.flat) if with_moments else None
-        self.step_dev = torch.zeros(1, dtype=torch.float32, device=self.device)
+        self.step_dev = torch.zeros(2, dtype=torch.float32, device=self.device)
 
     # ---- collectives --------------------------------------------------------------------
     def allreduce_grads(self, scale: float | None = None, stream=None) -> None:

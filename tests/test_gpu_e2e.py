@@ -150,6 +150,7 @@ def test_pipelined_feed_matches_plain_loop(tmp_path, graph):
                                           max_keys_per_batch=1 << 14)
         torch.manual_seed(3)
         ds = _ds(tmp_path, 6, 4, 128, 32, files=2)     # 256 instances -> 8 full batches
+        ds.set_thread(1)                               # one reader: the record order is reproducible
         model = DeepFM(num_slots=6, embedx_dim=8, dense_dim=4, hidden=(32, 16)).cuda()
         tr = CTRTrainer(model, box, TrainerConfig(dense_lr=1e-2))
         ds.load_into_memory()

@@ -447,7 +447,7 @@ def test_dense_helper_kernels():
     p = torch.randn(10000, device=dev())
     pt = p.clone().requires_grad_(True)
     opt = torch.optim.Adam([pt], lr=1e-3)
-    m, v, step = torch.zeros_like(p), torch.zeros_like(p), torch.zeros(1, device=dev())
+    m, v, step = torch.zeros_like(p), torch.zeros_like(p), torch.zeros(2, device=dev())
     for _ in range(3):
         g = torch.randn_like(p)
         pt.grad = g.clone()
@@ -523,3 +523,52 @@ def test_symm_collectives_virtual_ranks(nranks):
     SymmetricBuffer.collective_emu(bufs, 0, n, 1.0, "broadcast", root=1)
     for b in bufs:
         assert torch.equal(b.tensor[:n], data[0])
+
+
+def test_ctr_head_matches_torch():
+    from paddlebox_b200.ops import functional as F
+    torch.manual_seed(0)
+    B = 1000
+    tower = torch.randn(B, 1, device=dev(), requires_grad=True)
+    extra = torch.randn(B, device=dev(), requires_grad=True)
+    bias = torch.randn(1, device=dev(), requires_grad=True)
+    dense = torch.rand(B, 5, device=dev())
+    dense[:, 0] = (dense[:, 0] < 0.3).float()
+    label = dense[:, 0]                      # strided column, as the models pass it
+    loss, pred = F.ctr_head(tower, label, extra=extra, bias=bias)
+    (loss * 2.0).backward()
+    t2, e2, b2 = [x.detach().clone().requires_grad_(True) for x in (tower, extra, bias)]
+    z = t2.view(-1) + e2 + b2
+    ref = torch.nn.functional.binary_cross_entropy_with_logits(z, label)
+    (ref * 2.0).backward()
+    assert torch.allclose(loss, ref, rtol=1e-5, atol=1e-6)
+    assert torch.allclose(pred, torch.sigmoid(z), atol=1e-6)
+    assert torch.allclose(tower.grad, t2.grad, atol=1e-7) and torch.allclose(extra.grad, e2.grad, atol=1e-7)
+    assert torch.allclose(bias.grad, b2.grad, rtol=1e-4, atol=1e-6)
+    # tower only
+    t3 = tower.detach().clone().requires_grad_(True)
+    l3, _ = F.ctr_head(t3, label)
+    l3.backward()
+    t4 = tower.detach().clone().requires_grad_(True)
+    torch.nn.functional.binary_cross_entropy_with_logits(t4.view(-1), label).backward()
+    assert torch.allclose(t3.grad, t4.grad, atol=1e-7)
+
+
+def test_cast_transpose_multi():
+    from paddlebox_b200.ops.mlp import cast_transpose_multi, _pad8
+    torch.manual_seed(1)
+    shapes = [(512, 507), (256, 512), (1, 128), (77, 33)] + [(40, 9)] * 10      # > 12 tensors: two launches
+    items, refs = [], []
+    for i, (M, K) in enumerate(shapes):
+        x = torch.randn(M, K, device=dev())
+        out = torch.zeros(M, _pad8(K), dtype=torch.bfloat16, device=dev()) if i != 2 else None
+        out_t = torch.zeros(K, _pad8(M), dtype=torch.bfloat16, device=dev()) if i != 3 else None
+        items.append((x, out, out_t))
+    cast_transpose_multi(items)
+    for (x, out, out_t) in items:
+        M, K = x.shape
+        xb = x.to(torch.bfloat16)
+        if out is not None:
+            assert torch.equal(out[:, :K], xb) and float(out[:, K:].abs().sum()) == 0
+        if out_t is not None:
+            assert torch.equal(out_t[:, :M], xb.t())
