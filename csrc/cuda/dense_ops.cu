@@ -42,28 +42,47 @@ struct CastTransposeBatch {
   int ld[PBX_CT_MAX], M[PBX_CT_MAX], K[PBX_CT_MAX], ldo[PBX_CT_MAX], ldt[PBX_CT_MAX];
 };
 
-__global__ void k_cast_transpose_multi(const __grid_constant__ CastTransposeBatch b) {
-  __shared__ float tile[32][33];
+__global__ void __launch_bounds__(256)
+k_cast_transpose_multi(const __grid_constant__ CastTransposeBatch b) {
+  // 64x64 tiles: coalesced fp32 reads into shared memory, then both outputs leave as packed
+  // bf16x2 (128 bytes per warp row)
+  __shared__ float tile[64][65];
   int t = 0;
   while (t < b.n - 1 && (int)blockIdx.x >= b.tile_end[t]) ++t;
   const int local = blockIdx.x - (t ? b.tile_end[t - 1] : 0);
   const int M = b.M[t], K = b.K[t], ld = b.ld[t], ldo = b.ldo[t], ldt = b.ldt[t];
-  const int tk = (K + 31) / 32;
-  const int m0 = (local / tk) * 32, k0 = (local % tk) * 32;
+  const int tk = (K + 63) / 64;
+  const int m0 = (local / tk) * 64, k0 = (local % tk) * 64;
   const float* __restrict__ x = b.x[t];
   __nv_bfloat16* __restrict__ out = b.out[t];
   __nv_bfloat16* __restrict__ out_t = b.out_t[t];
-  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
-    int m = m0 + r, k = k0 + threadIdx.x;
-    float v = (m < M && k < K) ? x[(int64_t)m * ld + k] : 0.f;
-    tile[r][threadIdx.x] = v;
-    if (out && m < M && k < K) out[(int64_t)m * ldo + k] = __float2bfloat16(v);
+  const int tx = threadIdx.x, ty = threadIdx.y;
+#pragma unroll
+  for (int r = ty; r < 64; r += 8) {
+    const int m = m0 + r;
+    const float* xr = x + (int64_t)m * ld + k0;
+    tile[r][tx] = (m < M && k0 + tx < K) ? __ldg(xr + tx) : 0.f;
+    tile[r][tx + 32] = (m < M && k0 + tx + 32 < K) ? __ldg(xr + tx + 32) : 0.f;
   }
-  if (!out_t) return;
   __syncthreads();
-  for (int r = threadIdx.y; r < 32; r += blockDim.y) {
-    int k = k0 + r, m = m0 + threadIdx.x;
-    if (k < K && m < M) out_t[(int64_t)k * ldt + m] = __float2bfloat16(tile[threadIdx.x][r]);
+  if (out) {
+    // pad columns [K, ldo) inside the tile are written as zeros (operands of a TMA-fed GEMM)
+#pragma unroll
+    for (int r = ty; r < 64; r += 8) {
+      const int m = m0 + r, k = k0 + 2 * tx;
+      if (m < M && k < ldo)
+        *reinterpret_cast<__nv_bfloat162*>(out + (int64_t)m * ldo + k) =
+            __floats2bfloat162_rn(tile[r][2 * tx], tile[r][2 * tx + 1]);
+    }
+  }
+  if (out_t) {
+#pragma unroll
+    for (int r = ty; r < 64; r += 8) {
+      const int k = k0 + r, m = m0 + 2 * tx;
+      if (k < K && m < ldt)
+        *reinterpret_cast<__nv_bfloat162*>(out_t + (int64_t)k * ldt + m) =
+            __floats2bfloat162_rn(tile[2 * tx][r], tile[2 * tx + 1][r]);
+    }
   }
 }
 
@@ -148,41 +167,79 @@ __global__ void k_sigmoid_logloss(const float* __restrict__ logit, const float* 
 
 // CTR head in one pass: logit = tower + extra + bias; pred = sigmoid(logit); mean log-loss;
 // dlogit = (pred - label) / B kept for the backward.  Replaces three adds, a copy and the loss op.
-__global__ void k_ctr_head_fwd(const float* __restrict__ tower, int ld_tower, const float* __restrict__ extra,
-                               const float* __restrict__ bias, const float* __restrict__ label, int ld_label, int B,
-                               float* __restrict__ pred, float* __restrict__ loss_sum,
-                               float* __restrict__ dlogit) {
+// ONE block: the loss is reduced in the block and written (not accumulated), so no zero-fill
+// launch precedes it and the sum is deterministic.
+__device__ __forceinline__ float pbx_block_sum_1024(float v, float* red) {
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+  __syncthreads();
+  float t = threadIdx.x < (blockDim.x >> 5) ? red[threadIdx.x] : 0.f;
+  if (threadIdx.x < 32)
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+  return t;   // valid in thread 0
+}
+
+__global__ void __launch_bounds__(1024)
+k_ctr_head_fwd(const float* __restrict__ tower, int ld_tower, const float* __restrict__ extra,
+               const float* __restrict__ bias, const float* __restrict__ label, int ld_label, int B,
+               float* __restrict__ pred, float* __restrict__ loss_out, float* __restrict__ dlogit) {
+  __shared__ float red[32];
   float local = 0.f;
   const float bv = bias ? bias[0] : 0.f;
   const float invB = 1.f / (float)B;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < B; i += gridDim.x * blockDim.x) {
-    float z = tower[(int64_t)i * ld_tower] + bv;
-    if (extra) z += extra[i];
-    const float y = label[(int64_t)i * ld_label];
-    const float p = 1.f / (1.f + __expf(-z));
-    pred[i] = p;
-    local += fmaxf(z, 0.f) - z * y + log1pf(__expf(-fabsf(z)));
-    dlogit[i] = (p - y) * invB;
+  for (int i0 = threadIdx.x; i0 < B; i0 += 4 * blockDim.x) {
+    float zt[4], ze[4], yy[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {               // all loads of four elements in flight together
+      const int i = i0 + u * blockDim.x;
+      const bool ok = i < B;
+      zt[u] = ok ? __ldg(tower + (int64_t)i * ld_tower) : 0.f;
+      ze[u] = (ok && extra) ? __ldg(extra + i) : 0.f;
+      yy[u] = ok ? __ldg(label + (int64_t)i * ld_label) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * blockDim.x;
+      if (i >= B) break;
+      const float z = zt[u] + ze[u] + bv, y = yy[u];
+      const float p = 1.f / (1.f + __expf(-z));
+      pred[i] = p;
+      local += fmaxf(z, 0.f) - z * y + log1pf(__expf(-fabsf(z)));
+      dlogit[i] = (p - y) * invB;
+    }
   }
-  for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
-  if ((threadIdx.x & 31) == 0) atomicAdd(loss_sum, local * invB);
+  const float tot = pbx_block_sum_1024(local, red);
+  if (threadIdx.x == 0) loss_out[0] = tot * invB;
 }
 
-// backward of the head: every logit term receives gloss * dlogit; the bias its sum.
-__global__ void k_ctr_head_bwd(const float* __restrict__ dlogit, const float* __restrict__ gloss, int B,
-                               float* __restrict__ d_tower, float* __restrict__ d_extra,
-                               float* __restrict__ d_bias) {
+// backward of the head: every logit term receives gloss * dlogit; the bias its sum (written, or
+// added to an existing gradient when `accumulate`).
+__global__ void __launch_bounds__(1024)
+k_ctr_head_bwd(const float* __restrict__ dlogit, const float* __restrict__ gloss, int B,
+               float* __restrict__ d_tower, float* __restrict__ d_extra, float* __restrict__ d_bias,
+               int accumulate) {
+  __shared__ float red[32];
   const float g = gloss[0];
   float local = 0.f;
-  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < B; i += gridDim.x * blockDim.x) {
-    const float d = dlogit[i] * g;
-    if (d_tower) d_tower[i] = d;
-    if (d_extra) d_extra[i] = d;
-    local += d;
+  for (int i0 = threadIdx.x; i0 < B; i0 += 4 * blockDim.x) {
+    float dv[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * blockDim.x;
+      dv[u] = i < B ? __ldg(dlogit + i) * g : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = i0 + u * blockDim.x;
+      if (i >= B) break;
+      if (d_tower) d_tower[i] = dv[u];
+      if (d_extra) d_extra[i] = dv[u];
+      local += dv[u];
+    }
   }
   if (d_bias) {
-    for (int o = 16; o > 0; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
-    if ((threadIdx.x & 31) == 0) atomicAdd(d_bias, local);
+    const float tot = pbx_block_sum_1024(local, red);
+    if (threadIdx.x == 0) d_bias[0] = accumulate ? d_bias[0] + tot : tot;
   }
 }
 
@@ -190,49 +247,71 @@ __global__ void k_ctr_head_bwd(const float* __restrict__ dlogit, const float* __
 //   x: [B, ldx], slot s occupies columns [s*E, (s+1)*E); column `wcol` is the first-order
 //   weight, columns [vcol, vcol+D) the factor vector.
 //   fm[b] = sum_s w_s + 0.5 * sum_d ((sum_s v_sd)^2 - sum_s v_sd^2)
-__global__ void k_fm_fwd(const float* __restrict__ x, int ldx, int B, int S, int E, int wcol, int vcol, int D,
-                         float* __restrict__ fm) {
-  const int warps = (gridDim.x * blockDim.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  for (int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < B; b += warps) {
+// One warp per row; the row (S*E floats) is read ONCE with coalesced loads into shared memory,
+// per-dimension sums are formed by lanes [0, D) from the shared copy.
+#define PBX_FM_WARPS 8
+__global__ void __launch_bounds__(PBX_FM_WARPS * 32)
+k_fm_fwd(const float* __restrict__ x, int ldx, int B, int S, int E, int wcol, int vcol, int D,
+         float* __restrict__ fm) {
+  extern __shared__ float s_fm[];
+  const int W = S * E;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  float* srow = s_fm + wib * (W + 32);
+  const int nw = blockDim.x >> 5;
+  const int warps = gridDim.x * nw;
+  for (int b = blockIdx.x * nw + wib; b < B; b += warps) {
     const float* row = x + (int64_t)b * ldx;
+    for (int e = lane; e < W; e += 32) srow[e] = __ldg(row + e);
+    __syncwarp();
     float acc = 0.f;
     for (int d = lane; d < D; d += 32) {
       float sv = 0.f, sq = 0.f;
       for (int s = 0; s < S; ++s) {
-        float v = row[s * E + vcol + d];
+        const float v = srow[s * E + vcol + d];
         sv += v;
         sq += v * v;
       }
       acc += 0.5f * (sv * sv - sq);
     }
-    for (int s = lane; s < S; s += 32) acc += row[s * E + wcol];
+    for (int s = lane; s < S; s += 32) acc += srow[s * E + wcol];
     for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
     if (lane == 0) fm[b] = acc;
+    __syncwarp();
   }
 }
-// dx[b, s*E + wcol] += g[b];  dx[b, s*E+vcol+d] += g[b] * (sum_s' v_s'd - v_sd)
-__global__ void k_fm_bwd(const float* __restrict__ x, int ldx, const float* __restrict__ g, int B, int S, int E,
-                         int wcol, int vcol, int D, float* __restrict__ dx, int lddx, int accumulate) {
-  const int warps = (gridDim.x * blockDim.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  for (int b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < B; b += warps) {
+// dx[b, s*E + wcol] += g[b];  dx[b, s*E+vcol+d] += g[b] * (sum_s' v_s'd - v_sd); other columns of
+// the slot block get 0 (or stay, when accumulating).  Row in and gradient row out are coalesced.
+__global__ void __launch_bounds__(PBX_FM_WARPS * 32)
+k_fm_bwd(const float* __restrict__ x, int ldx, const float* __restrict__ g, int B, int S, int E,
+         int wcol, int vcol, int D, float* __restrict__ dx, int lddx, int accumulate) {
+  extern __shared__ float s_fm[];
+  const int W = S * E;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  float* srow = s_fm + wib * (W + 32 + D);
+  float* ssum = srow + W + 32;
+  const int nw = blockDim.x >> 5;
+  const int warps = gridDim.x * nw;
+  for (int b = blockIdx.x * nw + wib; b < B; b += warps) {
     const float* row = x + (int64_t)b * ldx;
     float* drow = dx + (int64_t)b * lddx;
-    const float gb = g[b];
+    for (int e = lane; e < W; e += 32) srow[e] = __ldg(row + e);
+    const float gb = __ldg(g + b);
+    __syncwarp();
     for (int d = lane; d < D; d += 32) {
       float sv = 0.f;
-      for (int s = 0; s < S; ++s) sv += row[s * E + vcol + d];
-      for (int s = 0; s < S; ++s) {
-        float gv = gb * (sv - row[s * E + vcol + d]);
-        float* o = drow + s * E + vcol + d;
-        *o = accumulate ? *o + gv : gv;
-      }
+      for (int s = 0; s < S; ++s) sv += srow[s * E + vcol + d];
+      ssum[d] = sv;
     }
-    for (int s = lane; s < S; s += 32) {
-      float* o = drow + s * E + wcol;
-      *o = accumulate ? *o + gb : gb;
+    __syncwarp();
+    for (int e = lane; e < W; e += 32) {
+      const int c = e % E;
+      float gv;
+      if (c == wcol) gv = gb;
+      else if (c >= vcol && c < vcol + D) gv = gb * (ssum[c - vcol] - srow[e]);
+      else { if (accumulate) continue; gv = 0.f; }
+      drow[e] = accumulate ? drow[e] + gv : gv;
     }
+    __syncwarp();
   }
 }
 
@@ -367,6 +446,22 @@ __global__ void k_fill_u32(uint32_t* p, int64_t n, uint32_t v) {
 
 }  // namespace
 
+// warps per block / grid / dynamic shared memory of the FM kernels: as many warps (<= 8) as fit
+// 200 KB of per-warp row copies
+static int pbx_fm_geometry(const void* fn, int words_per_warp, int B, int* nw, int* blocks, size_t* smem) {
+  int w = PBX_FM_WARPS;
+  while (w > 1 && (size_t)w * words_per_warp * sizeof(float) > 200 * 1024) w >>= 1;
+  *smem = (size_t)w * words_per_warp * sizeof(float);
+  PBX_REQUIRE(*smem <= 200 * 1024, "fm: a row of %d floats does not fit in shared memory", words_per_warp);
+  if (*smem > 48 * 1024)
+    PBX_CUDA_CHECK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)*smem));
+  *nw = w;
+  int b = (B + w - 1) / w;
+  if (b > 148 * 8) b = 148 * 8;
+  *blocks = b;
+  return 0;
+}
+
 extern "C" {
 
 int pbx_cast_transpose(const float* x, int ld, int M, int K, void* out_bf16, int ldo, void* out_t, int ldt,
@@ -389,9 +484,11 @@ int pbx_cast_transpose_multi(int n, const float* const* x, const int* ld, const 
   int tiles = 0;
   for (int i = 0; i < n; ++i) {
     PBX_REQUIRE(M[i] > 0 && K[i] > 0, "cast_transpose_multi: empty tensor %d", i);
-    tiles += ((M[i] + 31) / 32) * ((K[i] + 31) / 32);
+    tiles += ((M[i] + 63) / 64) * ((K[i] + 63) / 64);
     b.tile_end[i] = tiles;
     b.x[i] = x[i]; b.out[i] = (__nv_bfloat16*)out[i]; b.out_t[i] = (__nv_bfloat16*)out_t[i];
+    PBX_REQUIRE((!out[i] || (ldo[i] & 1) == 0) && (!out_t[i] || (ldt[i] & 1) == 0),
+                "cast_transpose_multi: output leading dims must be even (tensor %d)", i);
     b.ld[i] = ld[i]; b.M[i] = M[i]; b.K[i] = K[i]; b.ldo[i] = ldo[i]; b.ldt[i] = ldt[i];
   }
   k_cast_transpose_multi<<<tiles, dim3(32, 8), 0, st>>>(b);
@@ -402,16 +499,15 @@ int pbx_cast_transpose_multi(int n, const float* const* x, const int* ld, const 
 int pbx_ctr_head_fwd(const float* tower, int ld_tower, const float* extra, const float* bias, const float* label,
                      int ld_label, int B, float* pred, float* loss_sum, float* dlogit, cudaStream_t st) {
   if (B <= 0) return 0;
-  k_ctr_head_fwd<<<pbx_grid_for(B, 256, 1), 256, 0, st>>>(tower, ld_tower, extra, bias, label, ld_label, B, pred,
-                                                          loss_sum, dlogit);
+  k_ctr_head_fwd<<<1, 1024, 0, st>>>(tower, ld_tower, extra, bias, label, ld_label, B, pred, loss_sum, dlogit);
   PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
 
 int pbx_ctr_head_bwd(const float* dlogit, const float* gloss, int B, float* d_tower, float* d_extra, float* d_bias,
-                     cudaStream_t st) {
+                     int accumulate, cudaStream_t st) {
   if (B <= 0) return 0;
-  k_ctr_head_bwd<<<pbx_grid_for(B, 256, 1), 256, 0, st>>>(dlogit, gloss, B, d_tower, d_extra, d_bias);
+  k_ctr_head_bwd<<<1, 1024, 0, st>>>(dlogit, gloss, B, d_tower, d_extra, d_bias, accumulate);
   PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
@@ -451,7 +547,11 @@ int pbx_sigmoid_logloss(const float* logit, const float* label, int B, float* pr
 
 int pbx_fm_fwd(const float* x, int ldx, int B, int S, int E, int wcol, int vcol, int D, float* fm, cudaStream_t st) {
   if (B <= 0) return 0;
-  k_fm_fwd<<<pbx_grid_for((long long)B * 32, 256, 8), 256, 0, st>>>(x, ldx, B, S, E, wcol, vcol, D, fm);
+  int nw, blocks;
+  size_t smem;
+  int rc = pbx_fm_geometry((const void*)k_fm_fwd, S * E + 32, B, &nw, &blocks, &smem);
+  if (rc) return rc;
+  k_fm_fwd<<<blocks, nw * 32, smem, st>>>(x, ldx, B, S, E, wcol, vcol, D, fm);
   PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
@@ -459,8 +559,11 @@ int pbx_fm_fwd(const float* x, int ldx, int B, int S, int E, int wcol, int vcol,
 int pbx_fm_bwd(const float* x, int ldx, const float* g, int B, int S, int E, int wcol, int vcol, int D, float* dx,
                int lddx, int accumulate, cudaStream_t st) {
   if (B <= 0) return 0;
-  k_fm_bwd<<<pbx_grid_for((long long)B * 32, 256, 8), 256, 0, st>>>(x, ldx, g, B, S, E, wcol, vcol, D, dx, lddx,
-                                                                     accumulate);
+  int nw, blocks;
+  size_t smem;
+  int rc = pbx_fm_geometry((const void*)k_fm_bwd, S * E + 32 + D, B, &nw, &blocks, &smem);
+  if (rc) return rc;
+  k_fm_bwd<<<blocks, nw * 32, smem, st>>>(x, ldx, g, B, S, E, wcol, vcol, D, dx, lddx, accumulate);
   PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }

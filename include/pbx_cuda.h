@@ -114,13 +114,13 @@ int pbx_adam_flat(float* p, float* g, float* m, float* v, int64_t n, float lr, f
 int pbx_sgd_flat(float* p, float* g, int64_t n, float lr, float grad_scale, int zero_grad, pbx_stream_t stream);
 int pbx_sigmoid_logloss(const float* logit, const float* label, int B, float* pred, float* loss_sum,
                         float* dlogit, float gscale, pbx_stream_t stream);
-/* fused CTR head: logit = tower[i*ld_tower] + extra[i] + bias[0]; pred, mean log-loss (added to
- * *loss_sum) and dlogit = (pred - label)/B in one pass; the backward scales dlogit by *gloss and
- * adds its sum to *d_bias.  extra / bias / d_* may be NULL. */
+/* fused CTR head: logit = tower[i*ld_tower] + extra[i] + bias[0]; pred, mean log-loss (written to
+ * *loss_out) and dlogit = (pred - label)/B in one single-block pass; the backward scales dlogit by
+ * *gloss and writes (accumulate: adds) its sum to *d_bias.  extra / bias / d_* may be NULL. */
 int pbx_ctr_head_fwd(const float* tower, int ld_tower, const float* extra, const float* bias, const float* label,
-                     int ld_label, int B, float* pred, float* loss_sum, float* dlogit, pbx_stream_t stream);
+                     int ld_label, int B, float* pred, float* loss_out, float* dlogit, pbx_stream_t stream);
 int pbx_ctr_head_bwd(const float* dlogit, const float* gloss, int B, float* d_tower, float* d_extra, float* d_bias,
-                     pbx_stream_t stream);
+                     int accumulate, pbx_stream_t stream);
 int pbx_fm_fwd(const float* x, int ldx, int B, int S, int E, int wcol, int vcol, int D, float* fm,
                pbx_stream_t stream);
 int pbx_fm_bwd(const float* x, int ldx, const float* g, int B, int S, int E, int wcol, int vcol, int D, float* dx,

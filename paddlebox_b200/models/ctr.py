@@ -124,9 +124,13 @@ class DeepFM(CTRModelBase):
     def forward(self, batch: SlotBatch):
         x, pooled, labels = self.features(batch)
         E = self.attrs.out_width(self.slot_width)
-        fm_in = x if self.data_norm is None else pooled     # x's leading columns are the pooled slots
-        fm = F.fm_interaction(fm_in, self.num_slots, E, 2, 3, self.embedx_dim)
-        loss, pred = F.ctr_head(self.tower(x), labels[:, 0], extra=fm, bias=self.bias)
+        if self.data_norm is None:
+            # x's leading columns are the pooled slots: tower and FM term share one autograd node
+            deep, fm = self.tower.forward_with_fm(x, self.num_slots, E, 2, 3, self.embedx_dim)
+        else:
+            fm = F.fm_interaction(pooled, self.num_slots, E, 2, 3, self.embedx_dim)
+            deep = self.tower(x)
+        loss, pred = F.ctr_head(deep, labels[:, 0], extra=fm, bias=self.bias)
         return loss, {"pred": pred, "label": labels[:, 0]}
 
 

@@ -190,7 +190,9 @@ def sigmoid_log_loss(logit: torch.Tensor, label: torch.Tensor):
 
 
 class _CtrHead(torch.autograd.Function):
-    """logit = tower + extra + bias -> (mean log-loss, pred) as one kernel forward, one backward."""
+    """logit = tower + extra + bias -> (mean log-loss, pred) as one kernel forward, one backward.
+    The bias gradient is added straight into ``bias.grad`` when that exists (as the towers do
+    with their weights), so autograd launches no accumulation kernel for it."""
 
     @staticmethod
     def forward(ctx, tower, extra, bias, label):
@@ -198,7 +200,7 @@ class _CtrHead(torch.autograd.Function):
         assert tower.dim() in (1, 2) and (tower.dim() == 1 or tower.shape[1] == 1)
         dev = tower.device
         pred = torch.empty(B, dtype=torch.float32, device=dev)
-        loss = torch.zeros((), dtype=torch.float32, device=dev)
+        loss = torch.empty((), dtype=torch.float32, device=dev)
         dlogit = torch.empty(B, dtype=torch.float32, device=dev)
         if extra is not None:
             extra = extra.contiguous()
@@ -208,22 +210,35 @@ class _CtrHead(torch.autograd.Function):
                                           N.stream_ptr()), "pbx_ctr_head_fwd")
         ctx.save_for_backward(dlogit)
         ctx.shape = tuple(tower.shape)
-        ctx.has = (extra is not None, bias is not None)
+        ctx.has_extra = extra is not None
+        ctx.bias = bias if (bias is not None and bias.requires_grad and bias.is_leaf) else None
+        ctx.bias_nonleaf = bias is not None and ctx.bias is None
         ctx.mark_non_differentiable(pred)
+        ctx.set_materialize_grads(False)
         return loss, pred
 
     @staticmethod
     def backward(ctx, gloss, gpred):
         (dlogit,) = ctx.saved_tensors
         B = dlogit.numel()
-        need_t, need_e, need_b = ctx.needs_input_grad[0], ctx.needs_input_grad[1] and ctx.has[0], \
-            ctx.needs_input_grad[2] and ctx.has[1]
-        d_tower = torch.empty(ctx.shape, dtype=torch.float32, device=dlogit.device) if need_t else None
-        d_extra = torch.empty(B, dtype=torch.float32, device=dlogit.device) if need_e else None
-        d_bias = torch.zeros(1, dtype=torch.float32, device=dlogit.device) if need_b else None
+        dev = dlogit.device
+        if gloss is None:
+            return None, None, None, None
+        need_t = ctx.needs_input_grad[0]
+        need_e = ctx.needs_input_grad[1] and ctx.has_extra
+        d_tower = torch.empty(ctx.shape, dtype=torch.float32, device=dev) if need_t else None
+        d_extra = torch.empty(B, dtype=torch.float32, device=dev) if need_e else None
+        d_bias_ret, d_bias_ptr, acc = None, None, 0
+        if ctx.bias is not None:
+            if ctx.bias.grad is not None:
+                d_bias_ptr, acc = ctx.bias.grad, 1          # in place: nothing returned to autograd
+            else:
+                d_bias_ret = d_bias_ptr = torch.empty(1, dtype=torch.float32, device=dev)
+        elif ctx.bias_nonleaf and ctx.needs_input_grad[2]:
+            d_bias_ret = d_bias_ptr = torch.empty(1, dtype=torch.float32, device=dev)
         N.check(N.cuda().pbx_ctr_head_bwd(N.ptr(dlogit), N.ptr(gloss.contiguous()), B, N.ptr(d_tower), N.ptr(d_extra),
-                                          N.ptr(d_bias), N.stream_ptr()), "pbx_ctr_head_bwd")
-        return d_tower, d_extra, d_bias, None
+                                          N.ptr(d_bias_ptr), acc, N.stream_ptr()), "pbx_ctr_head_bwd")
+        return d_tower, d_extra, d_bias_ret, None
 
 
 def ctr_head(tower: torch.Tensor, label: torch.Tensor, extra: torch.Tensor | None = None,

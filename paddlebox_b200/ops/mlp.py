@@ -103,16 +103,41 @@ class _Workspace:
 
 
 class _MLPFn(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, x, mod, *params):
-        ctx.mod = mod
-        ctx.x_requires_grad = x.requires_grad
-        return mod._forward_cuda(x, torch.is_grad_enabled() or True)
+    """The tower as one node.  With ``fm`` = (S, E, wcol, vcol, D) the node also evaluates the
+    DeepFM first/second-order term on the same input and, in backward, adds its gradient into
+    the tower's input gradient in place (no zero-fill + add passes for the second consumer)."""
 
     @staticmethod
-    def backward(ctx, dout):
-        dx = ctx.mod._backward_cuda(dout.contiguous(), ctx.x_requires_grad)
-        return (dx, None) + (None,) * (2 * len(ctx.mod.weights))
+    def forward(ctx, x, mod, fm, *params):
+        ctx.mod = mod
+        ctx.fm = fm
+        ctx.x_requires_grad = x.requires_grad
+        out = mod._forward_cuda(x, torch.is_grad_enabled() or True)
+        if fm is None:
+            return out
+        S, E, wcol, vcol, D = fm
+        xx = x if x.stride(1) == 1 else x.contiguous()
+        fm_out = torch.empty(x.shape[0], dtype=torch.float32, device=x.device)
+        N.check(N.cuda().pbx_fm_fwd(N.ptr(xx), xx.stride(0), x.shape[0], S, E, wcol, vcol, D, N.ptr(fm_out),
+                                    N.stream_ptr()), "pbx_fm_fwd")
+        ctx.save_for_backward(xx)
+        ctx.set_materialize_grads(False)
+        return out, fm_out
+
+    @staticmethod
+    def backward(ctx, dout, dfm=None):
+        mod = ctx.mod
+        nparam = 2 * len(mod.weights)
+        need_dx = ctx.x_requires_grad
+        if dout is None:                      # only the FM branch contributed
+            dout = torch.zeros(mod._cur.B, mod.dims[-1], dtype=torch.float32, device=mod.weights[0].device)
+        dx = mod._backward_cuda(dout.contiguous(), need_dx)
+        if ctx.fm is not None and dfm is not None and need_dx:
+            (xx,) = ctx.saved_tensors
+            S, E, wcol, vcol, D = ctx.fm
+            N.check(N.cuda().pbx_fm_bwd(N.ptr(xx), xx.stride(0), N.ptr(dfm.contiguous()), xx.shape[0], S, E, wcol, vcol,
+                                        D, N.ptr(dx), dx.stride(0), 1, N.stream_ptr()), "pbx_fm_bwd")
+        return (dx, None, None) + (None,) * nparam
 
 
 class FusedMLP(nn.Module):
@@ -174,6 +199,13 @@ class FusedMLP(nn.Module):
         self._versions = vers
 
     # ---- execution ------------------------------------------------------------
+    def forward_with_fm(self, x: torch.Tensor, num_slots: int, slot_width: int, wcol: int, vcol: int, dim: int):
+        """(tower(x), fm(x)): the tower and the DeepFM interaction term as ONE autograd node."""
+        if not x.is_cuda:
+            from . import reference as R
+            return self.forward(x), R.fm_fwd(x, num_slots, slot_width, wcol, vcol, dim)
+        return _MLPFn.apply(x, self, (num_slots, slot_width, wcol, vcol, dim), *self.weights, *self.biases)
+
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if not x.is_cuda:
             h = x
@@ -183,7 +215,7 @@ class FusedMLP(nn.Module):
                 if i < L - 1 or self.final_relu:
                     h = torch.relu(h)
             return h
-        return _MLPFn.apply(x, self, *self.weights, *self.biases)
+        return _MLPFn.apply(x, self, None, *self.weights, *self.biases)
 
     def _forward_cuda(self, x: torch.Tensor, training: bool) -> torch.Tensor:
         B = x.shape[0]

@@ -103,7 +103,7 @@ class _PullBoxSparse(torch.autograd.Function):
         if offset:
             dout = torch.nn.functional.pad(dout, (offset, 0))
         box.push_sparse_grad(batch.keys, ctx.restore, dout.contiguous(), batch.key2slot(), batch.batch_size)
-        return torch.zeros_like(_anchor(dout.device)), None, None, None, None
+        return None, None, None, None, None
 
 
 def pull_box_sparse(batch: SlotBatch, size: int | None = None, offset: int = 0,
@@ -167,7 +167,7 @@ class _SparseEmbeddingPool(torch.autograd.Function):
         box, batch, attrs = ctx.box, ctx.batch, ctx.attrs
         (cvm,) = ctx.saved_tensors
         B, S = batch.batch_size, batch.num_slots
-        nothing = (torch.zeros_like(_anchor(dout.device)), None, None, None, None, None)
+        nothing = (None, None, None, None, None, None)    # the anchor only keeps the node alive
         if box._test_mode:
             return nothing
         fused_ok = (dout.is_cuda and attrs.cvm_offset == 2 and attrs.embedx_concate_size == 1
