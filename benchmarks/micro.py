@@ -90,6 +90,27 @@ def bench_gemm(out, flush):
             print(out[-1], flush=True)
 
 
+def bench_wgrad_sweep(out, flush):
+    """wgrad shapes of the DeepFM tower: tile width x split-K sweep (atomics contention vs main-loop length)."""
+    from paddlebox_b200.ops.mlp import _pad8, gemm_bf16_tn
+    dev = torch.device("cuda")
+    for name, M, Nn, K in [("wgrad L0", 512, 508, 4096), ("wgrad L1", 256, 513, 4096), ("wgrad L2", 128, 257, 4096),
+                           ("dgrad L0 f32", 4096, 507, 512)]:
+        A = torch.randn(M, _pad8(K), device=dev).to(torch.bfloat16)
+        B = torch.randn(Nn, _pad8(K), device=dev).to(torch.bfloat16)
+        o32 = torch.zeros(M, Nn, device=dev)
+        for bn in (32, 64, 128):
+            for sk in (1, 2, 4, 8, 16):
+                if name.startswith("dgrad") and sk > 1:
+                    continue
+                fn = lambda: gemm_bf16_tn(A, B, M, Nn, K, out_f32=o32, accumulate=sk > 1 or name.startswith("wgrad"),
+                                          splitk=sk, block_n=bn)
+                us = timeit(fn, flush=flush)
+                ctas = ((M + 127) // 128) * ((Nn + bn - 1) // bn) * sk
+                out.append({"kernel": "gemm_sweep", "case": name, "bn": bn, "splitk": sk, "ctas": ctas, "us": round(us, 2)})
+                print(out[-1], flush=True)
+
+
 def bench_sparse(out, flush, keys_per_gpu=125_000_000, dim=16, B=4096, S=26, max_bag=5):
     from paddlebox_b200.ops.seqpool import SeqpoolAttrs, seqpool_cvm_forward
     from paddlebox_b200.ops.sparse_table import SparseTable, synthetic_key
@@ -177,6 +198,8 @@ def main():
     out = []
     if "gemm" in a.what:
         bench_gemm(out, flush)
+    if "wgrad_sweep" in a.what:
+        bench_wgrad_sweep(out, flush)
     if "sparse" in a.what:
         bench_sparse(out, flush, a.keys_per_gpu)
     if a.json:

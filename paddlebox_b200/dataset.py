@@ -331,8 +331,17 @@ class InMemoryDataset(DatasetBase):
             self.prepare_train(1)
         w = self._worker if worker is None else worker
         device = device or self._device
-        loader = _BatchLoader(self._native, w, device, prefetch, with_ins_id)
+        loader = _BatchLoader(self._native, w, device, prefetch, with_ins_id, self._want_meta(),
+                              getattr(self, "max_rank", 3))
         return iter(loader)
+
+    def _want_meta(self) -> bool:
+        """PV batches carry search_id / rank / cmatch and the rank-offset matrix when a rank-offset
+        variable was named (``set_rank_offset``) or logkeys are parsed."""
+        return bool(getattr(self, "rank_offset_name", "")) or bool(getattr(self, "parse_logkey", False))
+
+    def set_max_rank(self, max_rank: int):
+        self.max_rank = int(max_rank)
 
     def host_batches(self, worker: int | None = None, prefetch: int = 3, with_ins_id: bool = False):
         """Iterate this worker's batches as pinned, record-major :class:`~paddlebox_b200.feed.HostBatch`
@@ -340,7 +349,8 @@ class InMemoryDataset(DatasetBase):
         if self._prepared_workers == 0:
             self.prepare_train(1)
         w = self._worker if worker is None else worker
-        loader = _BatchLoader(self._native, w, torch.device("cuda"), prefetch, with_ins_id)
+        loader = _BatchLoader(self._native, w, torch.device("cuda"), prefetch, with_ins_id, self._want_meta(),
+                              getattr(self, "max_rank", 3))
         return loader.host_batches()
 
 
@@ -454,8 +464,10 @@ class _PinnedStage:
 
 
 class _BatchLoader:
-    def __init__(self, native: NativeDataset, worker: int, device: torch.device, prefetch: int, with_ins_id: bool):
+    def __init__(self, native: NativeDataset, worker: int, device: torch.device, prefetch: int, with_ins_id: bool,
+                 with_meta: bool = False, max_rank: int = 3):
         self.native, self.worker, self.device = native, worker, device
+        self.with_meta, self.max_rank = with_meta, max_rank
         self.S = native.n_sparse()
         self.Dd = native.dense_dim()
         self.nb = native.num_batches(worker)
@@ -490,9 +502,29 @@ class _BatchLoader:
                 # GPU: record-major (batch_build transposes on the device); CPU: slot-major directly
                 self.native.pack_batch(self.worker, b, st.keys_ptr, st.off_ptr, st.dense_ptr, not self.cuda)
                 ids = self.native.batch_ins_ids(self.worker, b) if self.with_ins_id else None
+                if self.with_meta:
+                    ids = (ids, self._meta(b, B))
                 self.q.put((b, B, n, st, ids))
         finally:
             self.q.put(None)
+
+    def _meta(self, b: int, B: int) -> dict:
+        """search_id / rank / cmatch of the batch's instances and the PV rank-offset matrix
+        (``GetRankOffset`` + ``CopyRankOffsetKernel``, data_feed.cc:3531-3591, data_feed.cu:1319-1369)."""
+        from .ops.ctr_ops import build_rank_offset
+        sid, rk, cm = self.native.batch_meta(self.worker, b, B)
+        sid_t = torch.from_numpy(sid.astype(np.int64))
+        rk_t = torch.from_numpy(rk.astype(np.int32))
+        return {"search_id": sid_t, "rank": rk_t, "cmatch": torch.from_numpy(cm.astype(np.int32)),
+                "rank_offset": build_rank_offset(sid_t, rk_t, self.max_rank)}
+
+    def _split(self, ids):
+        if self.with_meta:
+            ids, meta = ids
+            if self.cuda:
+                meta = {k: v.to(self.device, non_blocking=True) for k, v in meta.items()}
+            return ids, meta
+        return ids, None
 
     def host_batches(self):
         """Packed batches left in pinned memory (the staging buffer returns to the pool when the
@@ -505,9 +537,12 @@ class _BatchLoader:
             if item is None:
                 return
             b, B, n, st, ids = item
+            ids, meta = self._split(ids)
             k, o, d = st.views(n, B * (S + 1), B * Dd)
-            yield HostBatch(k, o, d.view(B, Dd) if Dd else None, B, S, n, ins_ids=ids,
-                            release=lambda st=st: self.free.put(st))
+            hb = HostBatch(k, o, d.view(B, Dd) if Dd else None, B, S, n, ins_ids=ids,
+                           release=lambda st=st: self.free.put(st))
+            hb.meta = meta
+            yield hb
 
     def __iter__(self):
         self.thread.start()
@@ -517,6 +552,7 @@ class _BatchLoader:
             if item is None:
                 return
             b, B, n, st, ids = item
+            ids, meta = self._split(ids)
             if self.cuda:
                 n_off = B * (S + 1)
                 k, o, d = st.views(n, n_off, B * Dd)
@@ -532,7 +568,7 @@ class _BatchLoader:
                                                  N.ptr(scratch), N.stream_ptr()), "pbx_batch_build")
                 ev = torch.cuda.Event()
                 ev.record()
-                batch = SlotBatch(keys[:n], lod, B, S, dd, n_keys=n, ins_ids=ids)
+                batch = SlotBatch(keys[:n], lod, B, S, dd, n_keys=n, ins_ids=ids, meta=meta)
                 batch._keepalive = (dk, do, scratch)
                 yield batch
                 ev.synchronize()   # staging buffer may be reused once its copies are done
@@ -540,6 +576,6 @@ class _BatchLoader:
             else:
                 k, o, d = st.views(n, S * B + 1, B * Dd)
                 batch = SlotBatch(k.clone(), o.clone(), B, S, d.clone().view(B, Dd) if Dd else None, n_keys=n,
-                                  ins_ids=ids)
+                                  ins_ids=ids, meta=meta)
                 self.free.put(st)
                 yield batch

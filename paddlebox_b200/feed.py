@@ -44,6 +44,7 @@ class HostBatch:
     n_keys: int
     ins_ids: Optional[list] = None
     release: Optional[Callable[[], None]] = None     # called once the H2D copies have completed
+    meta: Optional[dict] = None                      # search_id / rank / cmatch / rank_offset tensors
 
     def h2d_bytes(self) -> int:
         b = self.n_keys * 8 + self.offsets.numel() * 4
@@ -131,13 +132,14 @@ class PipelinedFeed:
             tgt.dense.copy_(s.dense, non_blocking=True)
         s.built.record(main)
         tgt.ins_ids = hb.ins_ids
+        tgt.meta = hb.meta
         if tgt is getattr(tr, "_static", None) and getattr(tr, "_graph", None) is not None and not tr.cfg.is_test:
             tr._graph.replay()
             tr.steps += 1
             loss = tr._graph_loss
         else:
             batch = SlotBatch(tgt.keys[:max(hb.n_keys, 1)], tgt.lod, B, S, tgt.dense, n_keys=hb.n_keys,
-                              ins_ids=hb.ins_ids)
+                              ins_ids=hb.ins_ids, meta=hb.meta)
             loss = tr._eager_step(batch)
         slot = i % self.RING
         self.loss_pin[slot:slot + 1].copy_(loss.detach().reshape(1), non_blocking=True)

@@ -48,20 +48,23 @@ def build_rank_offset(search_id: torch.Tensor, rank: torch.Tensor, max_rank: int
     are one page view; ranks are 1-based, ranks > max_rank are ignored."""
     n = search_id.numel()
     out = torch.full((n, 2 * max_rank + 1), -1, dtype=torch.int32)
-    sid, rk = search_id.tolist(), rank.tolist()
-    groups: dict = {}
-    for i, s in enumerate(sid):
-        groups.setdefault(s, []).append(i)
-    for rows in groups.values():
-        for i in rows:
-            if not (1 <= rk[i] <= max_rank):
-                continue
-            out[i, 0] = rk[i]
-            for j in rows:
-                if 1 <= rk[j] <= max_rank:
-                    k = rk[j] - 1
-                    out[i, 2 * k + 1] = rk[j]
-                    out[i, 2 * k + 2] = j
+    if n == 0:
+        return out
+    sid = search_id.reshape(-1).cpu()
+    rk = rank.reshape(-1).cpu().long()
+    valid = (rk >= 1) & (rk <= max_rank)
+    out[valid, 0] = rk[valid].int()
+    _, inv = torch.unique(sid, return_inverse=True)
+    rows = torch.arange(n)
+    # table[pv, k] = row of the page view's ad with rank k+1 (the last one if a rank repeats)
+    table = torch.full((int(inv.max()) + 1, max_rank), -1, dtype=torch.long)
+    order = rows[valid]
+    table.index_put_((inv[order], rk[order] - 1), order)
+    for k in range(max_rank):
+        j = table[inv, k]
+        has = (j >= 0) & valid
+        out[has, 2 * k + 1] = k + 1
+        out[has, 2 * k + 2] = j[has].int()
     return out
 
 

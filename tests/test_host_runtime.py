@@ -279,3 +279,44 @@ def test_async_dense_table():
     t.wait()
     p = t.pull()
     assert t.updates() >= 2 and torch.all(p < 1.0) and torch.allclose(p, p[0].expand(1000))
+
+
+def test_pv_batches_carry_rank_offset(tmp_path):
+    """logkey-parsed, PV-merged batches expose search_id / rank / cmatch and the rank-offset matrix."""
+    import torch
+    from paddlebox_b200.dataset import DatasetFactory
+    from paddlebox_b200.ops.ctr_ops import build_rank_offset
+    from tests.util_data import slot_vars, write_files
+    ds = DatasetFactory().create_dataset("InMemoryDataset")
+    ds.set_use_var(slot_vars(3, 2))
+    ds.set_batch_size(12)
+    ds.set_thread(1)
+    ds.set_parse_logkey(True)
+    ds.set_enable_pv_merge(True)
+    ds.set_rank_offset("rank_offset")
+    ds.set_filelist(write_files(str(tmp_path), n_files=1, lines_per_file=36, n_sparse=3, n_dense=2, key_space=30,
+                                logkey=True))
+    ds.load_into_memory()
+    ds.prepare_train(1)
+    seen = 0
+    for b in ds.batches(device=torch.device("cpu")):
+        m = b.meta
+        assert m is not None and m["rank_offset"].shape == (b.batch_size, 7)
+        sid, rk, ro = m["search_id"].tolist(), m["rank"].tolist(), m["rank_offset"]
+        # brute-force definition
+        for i in range(b.batch_size):
+            if not 1 <= rk[i] <= 3:
+                assert int(ro[i, 0]) == -1
+                continue
+            assert int(ro[i, 0]) == rk[i]
+            for k in range(3):
+                js = [j for j in range(b.batch_size) if sid[j] == sid[i] and rk[j] == k + 1]
+                if js:
+                    assert int(ro[i, 2 * k + 1]) == k + 1 and int(ro[i, 2 * k + 2]) in js
+                else:
+                    assert int(ro[i, 2 * k + 1]) == -1
+        seen += b.batch_size
+    assert seen == 36
+    # ranks outside [1, max_rank] are ignored
+    ro = build_rank_offset(torch.tensor([5, 5, 5]), torch.tensor([1, 9, 2]), 3)
+    assert ro[1].tolist() == [-1] * 7 and ro[0].tolist() == [1, 1, 0, 2, 2, -1, -1]
