@@ -16,6 +16,7 @@
 // Replaces the reference's cuBLAS calls (mul/fc phi kernels; scaled_fc_op.cu:214;
 // batch_fc_op.cu:243) — there is no tensor-core code in the reference.
 #include "common.cuh"
+#include "pbx_types.h"
 #include <cuda.h>
 #include <cudaTypedefs.h>
 
@@ -40,7 +41,7 @@ struct GemmEpilogue {
   int col_split;              // out_f32 (bias gradient from a ones row appended to the B operand)
   unsigned long long* ts;     // optional debug timeline of CTA (0,0,0): 8 globaltimer stamps
 };
-#define GEMM_TS(i) do { if (ep.ts && (blockIdx.x | blockIdx.y | blockIdx.z) == 0) ep.ts[i] = pbx_globaltimer(); } while (0)
+#define GEMM_TS(i) do { if (ep.ts && (bx | by | bz) == 0) ep.ts[i] = pbx_globaltimer(); } while (0)
 
 // ---------------- PTX wrappers ----------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -144,10 +145,10 @@ struct SmemLayout {
   static_assert(BM * (BN + 8) * 2 + BN * (BM + 32) * 2 <= STAGES * STAGE_BYTES, "staging tiles do not fit");
 };
 
+// One output tile (bx, by) of split bz of one GEMM problem; the whole CTA participates.
 template <int BN>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
-k_gemm_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, int M, int N,
-               int K, int kb_per_split, GemmEpilogue ep) {
+__device__ __forceinline__ void gemm_tile(const CUtensorMap* pmap_a, const CUtensorMap* pmap_b, int M, int N, int K,
+                                          int kb_per_split, const GemmEpilogue& ep, int bx, int by, int bz) {
   extern __shared__ uint8_t smem_raw[];
   using L = SmemLayout<BN>;
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -160,17 +161,17 @@ k_gemm_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int m0 = blockIdx.x * BM;
-  const int n0 = blockIdx.y * BN;
+  const int m0 = bx * BM;
+  const int n0 = by * BN;
   const int num_kb_total = (K + BK - 1) / BK;
-  const int kb_begin = blockIdx.z * kb_per_split;
+  const int kb_begin = bz * kb_per_split;
   const int kb_end = min(kb_begin + kb_per_split, num_kb_total);
   const int num_kb = kb_end - kb_begin;
   if (threadIdx.x == 0) GEMM_TS(0);
 
   if (warp == 0 && lane == 0) {
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_a) : "memory");
-    asm volatile("prefetch.tensormap [%0];" ::"l"(&map_b) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(pmap_a) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(pmap_b) : "memory");
     for (int s = 0; s < STAGES; ++s) {
       mbar_init(full_bar + s, 1);
       mbar_init(empty_bar + s, 1);
@@ -197,8 +198,8 @@ k_gemm_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
           uint8_t* sb = sa + L::A_BYTES;
           mbar_expect_tx(full_bar + s, (uint32_t)L::STAGE_BYTES);
           const int kc = (kb_begin + i) * BK;
-          tma_load_2d(sa, &map_a, full_bar + s, kc, m0);
-          tma_load_2d(sb, &map_b, full_bar + s, kc, n0);
+          tma_load_2d(sa, pmap_a, full_bar + s, kc, m0);
+          tma_load_2d(sb, pmap_b, full_bar + s, kc, n0);
         }
       }
     } else if (warp == 1) {
@@ -438,6 +439,39 @@ k_gemm_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant_
   if (threadIdx.x == 0) GEMM_TS(7);
 }
 
+template <int BN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+k_gemm_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, int M, int N,
+               int K, int kb_per_split, GemmEpilogue ep) {
+  gemm_tile<BN>(&map_a, &map_b, M, N, K, kb_per_split, ep, blockIdx.x, blockIdx.y, blockIdx.z);
+}
+
+// Several independent GEMM problems in ONE launch (all weight gradients of a tower; the experts of
+// an MMoE layer): a dependent launch costs ~1.7 us plus a cold pipeline fill per kernel, which is
+// comparable to the work of one tower-sized GEMM.  CTAs are numbered problem after problem.
+constexpr int GEMM_GROUP_MAX = 8;
+struct GroupedGemm {
+  CUtensorMap map_a[GEMM_GROUP_MAX];
+  CUtensorMap map_b[GEMM_GROUP_MAX];
+  GemmEpilogue ep[GEMM_GROUP_MAX];
+  int M[GEMM_GROUP_MAX], N[GEMM_GROUP_MAX], K[GEMM_GROUP_MAX], kb_per[GEMM_GROUP_MAX];
+  int gx[GEMM_GROUP_MAX], gy[GEMM_GROUP_MAX];
+  int cta_end[GEMM_GROUP_MAX];
+  int n;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+k_gemm_tcgen05_grouped(const __grid_constant__ GroupedGemm g) {
+  int p = 0;
+  while (p < g.n - 1 && (int)blockIdx.x >= g.cta_end[p]) ++p;
+  const int local = blockIdx.x - (p ? g.cta_end[p - 1] : 0);
+  const int bx = local % g.gx[p];
+  const int by = (local / g.gx[p]) % g.gy[p];
+  const int bz = local / (g.gx[p] * g.gy[p]);
+  gemm_tile<BN>(&g.map_a[p], &g.map_b[p], g.M[p], g.N[p], g.K[p], g.kb_per[p], g.ep[p], bx, by, bz);
+}
+
 // --------- plain SIMT kernel with the same contract: numerics cross-check / fallback ---------
 __global__ void k_gemm_simt(const __nv_bfloat16* __restrict__ A, int lda, const __nv_bfloat16* __restrict__ B,
                             int ldb, int M, int N, int K, GemmEpilogue ep) {
@@ -520,11 +554,68 @@ int launch_tc(const __nv_bfloat16* A, int lda, const __nv_bfloat16* B, int ldb, 
   return 0;
 }
 
+template <int BN>
+int launch_grouped(const PbxGemmProblem* pr, int n, cudaStream_t st) {
+  static GroupedGemm g;     // ~3 KB: filled on the host, passed by value
+  memset(&g, 0, sizeof(g));
+  g.n = n;
+  int ctas = 0;
+  for (int i = 0; i < n; ++i) {
+    const PbxGemmProblem& q = pr[i];
+    PBX_REQUIRE(q.M > 0 && q.N > 0 && q.K > 0, "grouped gemm: empty problem %d", i);
+    PBX_REQUIRE(((uintptr_t)q.A & 15) == 0 && ((uintptr_t)q.B & 15) == 0 && (q.lda & 7) == 0 && (q.ldb & 7) == 0,
+                "grouped gemm: problem %d needs 16B-aligned operands and leading dims that are multiples of 8", i);
+    int rc = make_map(&g.map_a[i], q.A, q.M, q.K, q.lda, BM);
+    if (rc) return rc;
+    rc = make_map(&g.map_b[i], q.B, q.N, q.K, q.ldb, BN);
+    if (rc) return rc;
+    const int num_kb = (q.K + BK - 1) / BK;
+    int splitk = q.splitk < 1 ? 1 : q.splitk;
+    if (splitk > num_kb) splitk = num_kb;
+    const int kb_per = (num_kb + splitk - 1) / splitk;
+    splitk = (num_kb + kb_per - 1) / kb_per;
+    if (splitk > 1)
+      PBX_REQUIRE(q.accumulate && q.out_f32 && !q.out_bf16 && !q.out_t && !q.relu && !q.bias && !q.mask,
+                  "grouped gemm: split-K needs a pure fp32 accumulate epilogue (problem %d)", i);
+    GemmEpilogue& ep = g.ep[i];
+    ep.bias = q.bias; ep.mask = (const __nv_bfloat16*)q.mask;
+    ep.out_bf16 = (__nv_bfloat16*)q.out_bf16; ep.out_t = (__nv_bfloat16*)q.out_t; ep.out_f32 = q.out_f32;
+    ep.ld_mask = q.ld_mask; ep.ld_out = q.ld_out; ep.ld_t = q.ld_t; ep.ld_f32 = q.ld_f32;
+    ep.relu = q.relu; ep.accumulate = q.accumulate; ep.alpha = q.alpha;
+    ep.col_out = q.col_out; ep.col_split = q.col_split; ep.ts = nullptr;
+    g.M[i] = q.M; g.N[i] = q.N; g.K[i] = q.K; g.kb_per[i] = kb_per;
+    g.gx[i] = (q.M + BM - 1) / BM;
+    g.gy[i] = (q.N + BN - 1) / BN;
+    ctas += g.gx[i] * g.gy[i] * splitk;
+    g.cta_end[i] = ctas;
+  }
+  static bool attr_set = false;
+  if (!attr_set) {
+    PBX_CUDA_CHECK(cudaFuncSetAttribute(k_gemm_tcgen05_grouped<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        SmemLayout<BN>::TOTAL));
+    attr_set = true;
+  }
+  k_gemm_tcgen05_grouped<BN><<<ctas, GEMM_THREADS, SmemLayout<BN>::TOTAL, st>>>(g);
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
+  return 0;
+}
+
 unsigned long long* g_gemm_ts = nullptr;   // device buffer of 8 stamps when the debug timeline is on
 
 }  // namespace
 
 extern "C" {
+
+int pbx_gemm_bf16_tn_grouped(const PbxGemmProblem* problems, int n, int block_n, cudaStream_t st) {
+  PBX_REQUIRE(n >= 1 && n <= GEMM_GROUP_MAX, "grouped gemm: %d problems (max %d)", n, GEMM_GROUP_MAX);
+  switch (block_n == 0 ? 64 : block_n) {
+    case 32: return launch_grouped<32>(problems, n, st);
+    case 64: return launch_grouped<64>(problems, n, st);
+    case 128: return launch_grouped<128>(problems, n, st);
+    default: PBX_REQUIRE(false, "grouped gemm: unsupported block_n %d", block_n);
+  }
+  return 0;
+}
 
 // Debug timeline of CTA (0,0,0) of the next tcgen05 GEMM launches: kernel entry, setup done, first
 // stage landed, last MMA issued, accumulator complete, epilogue registers done, stores issued, exit.

@@ -90,6 +90,8 @@ int pbx_key2slot(const int32_t* d_lod, int B, int S, int64_t n, int32_t* d_out, 
  * C = epilogue(alpha * A[M,K] . B[N,K]^T); A, B bf16 K-contiguous.
  * reference call sites: scaled_fc_op.cu:214, batch_fc_op.cu:243, rank_attention_op.cu:110,
  * phi mul/matmul/fc kernels (all cuBLAS). */
+/* n <= 8 independent problems in one launch (block_n in {32, 64, 128}; 0 = 64) */
+int pbx_gemm_bf16_tn_grouped(const PbxGemmProblem* problems, int n, int block_n, pbx_stream_t stream);
 /* debug: in-kernel timeline (8 globaltimer stamps of CTA 0) of the next tcgen05 GEMM launches */
 int pbx_gemm_debug_enable(int on);
 int pbx_gemm_debug_ts(unsigned long long* out8);

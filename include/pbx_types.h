@@ -106,6 +106,23 @@ typedef struct PbxSeqpoolParams {
   const float* trade_w;        /* tradew: device [N] or NULL */
 } PbxSeqpoolParams;
 
+/* One problem of a grouped GEMM launch (pbx_gemm_bf16_tn_grouped): the arguments of
+ * pbx_gemm_bf16_tn as a record.  All problems of a launch share the tile width. */
+typedef struct PbxGemmProblem {
+  const void* A;        /* bf16 [M, lda] */
+  const void* B;        /* bf16 [N, ldb] */
+  const float* bias;
+  const void* mask;
+  void* out_bf16;
+  void* out_t;
+  float* out_f32;
+  float* col_out;
+  int lda, ldb, M, N, K;
+  int ld_mask, ld_out, ld_t, ld_f32;
+  int relu, accumulate, splitk, col_split;
+  float alpha;
+} PbxGemmProblem;
+
 #ifdef __cplusplus
 }
 #endif

@@ -82,6 +82,13 @@ class SeqpoolParams(C.Structure):
                [("slot_threshold", C.c_void_p), ("trade_w", C.c_void_p)]
 
 
+class GemmProblem(C.Structure):
+    """Mirror of ``PbxGemmProblem`` (include/pbx_types.h)."""
+    _fields_ = [(n, C.c_void_p) for n in ("A", "B", "bias", "mask", "out_bf16", "out_t", "out_f32", "col_out")] + \
+               [(n, C.c_int) for n in ("lda", "ldb", "M", "N", "K", "ld_mask", "ld_out", "ld_t", "ld_f32", "relu",
+                                       "accumulate", "splitk", "col_split")] + [("alpha", C.c_float)]
+
+
 class NativeError(RuntimeError):
     pass
 

@@ -50,6 +50,28 @@ def gemm_bf16_tn(A: torch.Tensor, B: torch.Tensor, M: int, Nn: int, K: int, *, b
         gemm_impl() if impl is None else impl, N.ptr(col_out), col_split, N.stream_ptr()), "pbx_gemm_bf16_tn")
 
 
+def gemm_problem(A, B, M, Nn, K, *, bias=None, mask=None, out_bf16=None, out_t=None, out_f32=None, relu=False,
+                 accumulate=False, alpha=1.0, splitk=1, col_out=None, col_split: int = -1) -> N.GemmProblem:
+    """One entry of a grouped launch: the arguments of :func:`gemm_bf16_tn` as a record."""
+    def p(t):
+        return t.data_ptr() if t is not None else None
+
+    def ld(t):
+        return t.stride(0) if t is not None else 0
+    return N.GemmProblem(p(A), p(B), p(bias), p(mask), p(out_bf16), p(out_t), p(out_f32), p(col_out),
+                         A.stride(0), B.stride(0), M, Nn, K, ld(mask), ld(out_bf16), ld(out_t), ld(out_f32),
+                         int(relu), int(accumulate), splitk, col_split, alpha)
+
+
+def gemm_bf16_tn_grouped(problems, block_n: int = 64) -> None:
+    """Up to 8 independent GEMMs per launch (one shared tile width)."""
+    for i0 in range(0, len(problems), 8):
+        chunk = problems[i0:i0 + 8]
+        arr = (N.GemmProblem * len(chunk))(*chunk)
+        N.check(N.cuda().pbx_gemm_bf16_tn_grouped(arr, len(chunk), block_n, N.stream_ptr()),
+                "pbx_gemm_bf16_tn_grouped")
+
+
 def cast_transpose(x: torch.Tensor, out: torch.Tensor | None, out_t: torch.Tensor | None) -> None:
     """fp32 [M, K] -> bf16 ``out`` [M, >=K] and/or bf16 ``out_t`` [K, >=M]."""
     M, K = x.shape
@@ -247,6 +269,7 @@ class FusedMLP(nn.Module):
             dout = dout * (self._last_out > 0)
         cast_transpose(dout, ws.dZ[L - 1], ws.dZt[L - 1])
         dx = None
+        wgrads = []
         for l in range(L - 1, -1, -1):
             K, Nn = self.dims[l], self.dims[l + 1]
             w, b = self.weights[l], self.biases[l]
@@ -257,8 +280,10 @@ class FusedMLP(nn.Module):
             # wgrad: dW[N, K] += dZ^T[N, B] . (H^T[K, B])^T   (split-K over the batch)
             splitk = max(1, min(16, B // 512))
             # (the ones row of Ht makes output column K the bias gradient: no separate column-sum pass)
-            gemm_bf16_tn(ws.dZt[l], ws.Ht[l], Nn, K + 1, B, out_f32=w.grad, accumulate=True, splitk=splitk,
-                         col_out=b.grad, col_split=K)
+            # Weight gradients are off the critical path of the dgrad chain: they are collected
+            # and issued as ONE grouped launch once every dZ exists.
+            wgrads.append(gemm_problem(ws.dZt[l], ws.Ht[l], Nn, K + 1, B, out_f32=w.grad, accumulate=True,
+                                       splitk=splitk, col_out=b.grad, col_split=K))
             if l > 0:
                 # dgrad fused with the ReLU mask of the previous activation
                 gemm_bf16_tn(ws.dZ[l], self._wbt[l], B, K, Nn, mask=ws.H[l], out_bf16=ws.dZ[l - 1],
@@ -266,6 +291,13 @@ class FusedMLP(nn.Module):
             elif need_dx:
                 dx = torch.empty(B, K, dtype=torch.float32, device=dout.device)
                 gemm_bf16_tn(ws.dZ[0], self._wbt[0], B, K, Nn, out_f32=dx)
+        if gemm_impl() == 0:
+            gemm_bf16_tn_grouped(wgrads, block_n=64)
+        else:   # SIMT cross-check path: one problem at a time
+            for q in wgrads:
+                N.check(N.cuda().pbx_gemm_bf16_tn(q.A, q.lda, q.B, q.ldb, q.M, q.N, q.K, None, None, 0, None, 0, None, 0,
+                                                  C.c_void_p(q.out_f32), q.ld_f32, 0, 1, C.c_float(1.0), 1, 0, 1,
+                                                  C.c_void_p(q.col_out), q.col_split, N.stream_ptr()), "pbx_gemm_bf16_tn")
         return dx
 
 

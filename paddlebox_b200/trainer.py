@@ -106,7 +106,9 @@ class CTRTrainer:
             torch.cuda.synchronize(dev)
             self.store.mark_dirty()
             g = torch.cuda.CUDAGraph()
-            with torch.cuda.graph(g):
+            # thread_local: a loader thread that pins host memory while we capture must not
+            # invalidate the capture
+            with torch.cuda.graph(g, capture_error_mode="thread_local"):
                 loss = self._eager_step(static)
             self._graph, self._graph_loss = g, loss
             torch.cuda.synchronize(dev)

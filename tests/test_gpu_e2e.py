@@ -150,7 +150,8 @@ def test_pipelined_feed_matches_plain_loop(tmp_path, graph):
                                           max_keys_per_batch=1 << 14)
         torch.manual_seed(3)
         ds = _ds(tmp_path, 6, 4, 128, 32, files=2)     # 256 instances -> 8 full batches
-        ds.set_thread(1)                               # one reader: the record order is reproducible
+        ds.set_thread(1)                               # one reader and one merger: the record order
+        ds.set_merge_thread_num(1)                     # (hence every batch) is reproducible
         model = DeepFM(num_slots=6, embedx_dim=8, dense_dim=4, hidden=(32, 16)).cuda()
         tr = CTRTrainer(model, box, TrainerConfig(dense_lr=1e-2))
         ds.load_into_memory()
@@ -158,7 +159,7 @@ def test_pipelined_feed_matches_plain_loop(tmp_path, graph):
         ds.prepare_train(1)
         if graph:
             first = next(iter(ds.batches()))
-            assert tr.enable_cuda_graph(first, 1 << 14, warmup=1)
+            assert tr.enable_cuda_graph(first, 1 << 14, warmup=1), getattr(tr, "_graph_error", None)
         if pipelined:
             st = tr.train_host_batches(ds.host_batches())
             losses = st["losses"]
