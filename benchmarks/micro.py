@@ -90,6 +90,26 @@ def bench_gemm(out, flush):
             print(out[-1], flush=True)
 
 
+def bench_big_tiles(out):
+    """large GEMMs (MMoE wide expert layer): tile width 128 vs 256."""
+    from paddlebox_b200.ops.mlp import _pad8, gemm_bf16_tn
+    hbm, tf, src = peaks()
+    dev = torch.device("cuda")
+    for name, M, Nn, K in [("big", 8192, 8192, 8192), ("mmoe wide fwd", 4096, 8192, 20100),
+                           ("mmoe wide dgrad", 4096, 20100, 8192), ("mmoe wide wgrad", 8192, 20100, 4096)]:
+        A = torch.randn(M, _pad8(K), device=dev).to(torch.bfloat16)
+        B = torch.randn(Nn, _pad8(K), device=dev).to(torch.bfloat16)
+        ob = torch.zeros(M, _pad8(Nn), dtype=torch.bfloat16, device=dev)
+        for bn in (128, 256):
+            us = timeit(lambda: gemm_bf16_tn(A, B, M, Nn, K, out_bf16=ob, block_n=bn), iters=5, warmup=2)
+            fl = 2.0 * M * Nn * K
+            out.append({"kernel": "gemm_big", "case": name, "bn": bn, "us": round(us, 1),
+                        "tflops": round(fl / us / 1e6, 1), "frac_of_peak": round(fl / us / 1e6 / tf, 3)})
+            print(out[-1], flush=True)
+        us = timeit(lambda: torch.matmul(A, B.t()), iters=5, warmup=2)
+        print({"case": name, "cublas_us": round(us, 1), "cublas_tflops": round(2.0 * M * Nn * K / us / 1e6, 1)}, flush=True)
+
+
 def bench_wgrad_sweep(out, flush):
     """wgrad shapes of the DeepFM tower: tile width x split-K sweep (atomics contention vs main-loop length)."""
     from paddlebox_b200.ops.mlp import _pad8, gemm_bf16_tn
@@ -198,6 +218,8 @@ def main():
     out = []
     if "gemm" in a.what:
         bench_gemm(out, flush)
+    if "big_tiles" in a.what:
+        bench_big_tiles(out)
     if "wgrad_sweep" in a.what:
         bench_wgrad_sweep(out, flush)
     if "sparse" in a.what:

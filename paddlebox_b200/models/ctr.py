@@ -143,18 +143,20 @@ class MMoE(CTRModelBase):
         self.n_labels = num_tasks
         super().__init__(num_slots, embedx_dim, dense_dim, **kw)
         self.num_experts, self.num_tasks = num_experts, num_tasks
-        self.experts = GroupedMLP(num_experts, [self.input_width, *expert_hidden], final_relu=True, name="expert")
-        self.gates = nn.ModuleList([FusedMLP([self.input_width, num_experts], name=f"gate{t}")
-                                    for t in range(num_tasks)])
+        # the gate logits of every task ride on the experts' wide first layer: ONE bf16 copy of
+        # x, one forward GEMM, one input-gradient GEMM for experts and gates together
+        self.experts = GroupedMLP(num_experts, [self.input_width, *expert_hidden], final_relu=True, name="expert",
+                                  extra_linear=num_tasks * num_experts)
         self.towers = nn.ModuleList([FusedMLP([expert_hidden[-1], *tower_hidden, 1], name=f"tower{t}")
                                      for t in range(num_tasks)])
 
     def forward(self, batch: SlotBatch):
         x, _, labels = self.features(batch)
-        ex = self.experts(x)                                   # [E, B, H]
+        ex, gate_logits = self.experts(x)                      # [E, B, H], [B, T*E]
+        gate_logits = gate_logits.view(-1, self.num_tasks, self.num_experts)
         losses, preds = [], []
         for t in range(self.num_tasks):
-            g = torch.softmax(self.gates[t](x), dim=1)         # [B, E]
+            g = torch.softmax(gate_logits[:, t], dim=1)        # [B, E]
             mix = torch.einsum("be,ebh->bh", g, ex)
             l, p = F.ctr_head(self.towers[t](mix), labels[:, t])
             losses.append(l)

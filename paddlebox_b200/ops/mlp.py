@@ -282,8 +282,14 @@ class FusedMLP(nn.Module):
             # (the ones row of Ht makes output column K the bias gradient: no separate column-sum pass)
             # Weight gradients are off the critical path of the dgrad chain: they are collected
             # and issued as ONE grouped launch once every dZ exists.
-            wgrads.append(gemm_problem(ws.dZt[l], ws.Ht[l], Nn, K + 1, B, out_f32=w.grad, accumulate=True,
-                                       splitk=splitk, col_out=b.grad, col_split=K))
+            if ((Nn + 127) // 128) * ((K + 128) // 128) >= 148:
+                # already a full wave of output tiles: no split-K (no contended atomics), own
+                # launch with the wide 128x256 tile
+                gemm_bf16_tn(ws.dZt[l], ws.Ht[l], Nn, K + 1, B, out_f32=w.grad, accumulate=True, splitk=1,
+                             col_out=b.grad, col_split=K)
+            else:
+                wgrads.append(gemm_problem(ws.dZt[l], ws.Ht[l], Nn, K + 1, B, out_f32=w.grad, accumulate=True,
+                                           splitk=splitk, col_out=b.grad, col_split=K))
             if l > 0:
                 # dgrad fused with the ReLU mask of the previous activation
                 gemm_bf16_tn(ws.dZ[l], self._wbt[l], B, K, Nn, mask=ws.H[l], out_bf16=ws.dZ[l - 1],
@@ -291,7 +297,9 @@ class FusedMLP(nn.Module):
             elif need_dx:
                 dx = torch.empty(B, K, dtype=torch.float32, device=dout.device)
                 gemm_bf16_tn(ws.dZ[0], self._wbt[0], B, K, Nn, out_f32=dx)
-        if gemm_impl() == 0:
+        if not wgrads:
+            pass
+        elif gemm_impl() == 0:
             gemm_bf16_tn_grouped(wgrads, block_n=64)
         else:   # SIMT cross-check path: one problem at a time
             for q in wgrads:
@@ -302,23 +310,62 @@ class FusedMLP(nn.Module):
 
 
 class GroupedMLP(nn.Module):
-    """``num`` towers of identical shape applied to the same (or per-tower) input; outputs
-    stacked as [num, B, out].  Expert towers of MMoE / the reference's ``batch_fc``."""
+    """``num`` towers of identical shape; outputs stacked as [num, B, out].  Expert towers of
+    MMoE / the reference's ``batch_fc`` (operators/batch_fc_op.cu:243).
 
-    def __init__(self, num: int, dims, final_relu: bool = True, name: str = "expert", seed: int | None = None):
+    With a SHARED input (x [B, in], the MMoE case) the first layers of all towers are one wide
+    layer ``in -> num*h1``: one forward GEMM with N = num*h1, one dgrad GEMM with K = num*h1 that
+    produces the input gradient already summed over the towers, one wgrad GEMM — instead of
+    ``num`` skinny GEMMs and ``num`` input-gradient tensors of B x in floats added by autograd.
+    The remaining layers are block-diagonal and run per tower on column slices of the wide
+    activation.  With per-tower inputs (x [num, B, in]) the towers are independent."""
+
+    def __init__(self, num: int, dims, final_relu: bool = True, name: str = "expert", seed: int | None = None,
+                 shared_input: bool = True, extra_linear: int = 0):
+        """``extra_linear`` > 0 (shared input only): that many further LINEAR output columns ride on
+        the wide first layer (the MMoE gate logits) — ``forward`` then returns (stacked, extra)."""
         super().__init__()
-        self.towers = nn.ModuleList([FusedMLP(dims, final_relu=final_relu, name=f"{name}{i}",
-                                              seed=None if seed is None else seed + i) for i in range(num)])
+        self.num, self.dims, self.shared_input, self.extra = num, list(dims), shared_input, extra_linear
+        self.first_relu = len(dims) > 2 or final_relu
+        if shared_input:
+            self.first = FusedMLP([dims[0], num * dims[1] + extra_linear],
+                                  final_relu=self.first_relu and extra_linear == 0, name=f"{name}_l0", seed=seed)
+            # re-draw each tower's block with the fan-in bound of a single tower layer (same init law)
+            rest = dims[1:]
+            self.towers = nn.ModuleList([FusedMLP(rest, final_relu=final_relu, name=f"{name}{i}",
+                                                  seed=None if seed is None else seed + 1 + i)
+                                         for i in range(num)]) if len(rest) > 1 else None
+        else:
+            self.first = None
+            self.towers = nn.ModuleList([FusedMLP(dims, final_relu=final_relu, name=f"{name}{i}",
+                                                  seed=None if seed is None else seed + i) for i in range(num)])
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        if x.dim() == 3:
-            return torch.stack([t(x[i]) for i, t in enumerate(self.towers)], 0)
-        return torch.stack([t(x) for t in self.towers], 0)
+        if self.first is None:
+            if x.dim() == 3:
+                return torch.stack([t(x[i]) for i, t in enumerate(self.towers)], 0)
+            return torch.stack([t(x) for t in self.towers], 0)
+        assert x.dim() == 2, "shared-input GroupedMLP takes x [B, in]"
+        h = self.first(x)                                    # [B, num*h1 (+ extra)]
+        extra = None
+        if self.extra:
+            h, extra = torch.split(h, [self.num * self.dims[1], self.extra], dim=1)
+            if self.first_relu:
+                h = torch.relu(h)
+        parts = torch.split(h, self.dims[1], dim=1)          # backward = one concat, no zero-fills
+        if self.towers is None:
+            out = torch.stack(parts, 0)
+        else:
+            out = torch.stack([t(p) for t, p in zip(self.towers, parts)], 0)
+        return (out, extra) if self.extra else out
+
+    def dense_towers(self):
+        return ([self.first] if self.first is not None else []) + (list(self.towers) if self.towers is not None else [])
 
     def mark_weights_dirty(self):
-        for t in self.towers:
+        for t in self.dense_towers():
             t.mark_weights_dirty()
 
     def named_dense_params(self):
-        for t in self.towers:
+        for t in self.dense_towers():
             yield from t.named_dense_params()
