@@ -19,6 +19,7 @@
 // of one cooperative grid on one GPU ("virtual ranks"); the cross-rank barrier then is
 // the grid barrier.  The per-rank code is identical.
 #include "sparse_a2a.cuh"
+#include "symm.cuh"
 #include <cooperative_groups.h>
 #include <vector>
 namespace cg = cooperative_groups;
@@ -55,6 +56,12 @@ struct PbxPushArgs {
   int hidden;
   int mode;
   float grad_scale;         // -batch_size (box_wrapper.cu:404-410)
+  // optional: the data-parallel dense-gradient allreduce rides on this kernel's barriers.  After
+  // the ship barrier every rank's dense gradients are final and visible; each rank reduces its
+  // slice from all peers, scales it, stores it to all peers, and one more barrier ends the kernel.
+  const PbxSymmDev* dense_ctx;
+  int64_t dense_off, dense_n;
+  float dense_scale;
 };
 struct PbxPushArgsN { PbxPushArgs a[PBX_MAX_RANKS]; };
 
@@ -190,13 +197,22 @@ k_sparse_pull(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPullArgsN args)
     const int PS = c.pull_stride;
     const int chunks = PS >> 2;
     const float4 zero4 = make_float4(0.f, 0.f, 0.f, 0.f);
-    for (int s = 0; s < R; ++s) {
+    // All-to-all without incast: the warps are split into R groups, group g serves requester
+    // (rank + 1 + g) % R, so at any moment every owner is writing to every requester at the same
+    // rate (with "everybody serves requester 0 first" the eight owners would pile onto one GPU's
+    // NVLink ingress while the other seven sat idle).
+    if (lb == 0 && tid < R) c.serve_cnt[tid] = min(__ldcg(c.mail_cnt[c.rank] + tid), cap);
+    const int nper = nwarps >= R ? nwarps / R : nwarps;
+    const int grp = nwarps >= R ? warp % R : 0;
+    const int widx = nwarps >= R ? warp / R : warp;
+    for (int sr = 0; sr < (nwarps >= R ? 1 : R); ++sr) {
+      if (nwarps >= R && widx >= nper) break;
+      const int s = (c.rank + 1 + grp + sr) % R;
       const uint32_t cnt = min(__ldcg(c.mail_cnt[c.rank] + s), cap);
-      if (lb == 0 && tid == 0) c.serve_cnt[s] = cnt;
       const uint64_t* mk = c.mail_keys[c.rank] + (uint64_t)s * cap;
       uint32_t* mrow = c.mail_row + (uint64_t)s * cap;
       float* dst = c.pull_vals[s] + (uint64_t)c.rank * cap * PS;  // requester s, my region
-      for (uint32_t j0 = (uint32_t)warp * 32u; j0 < cnt; j0 += (uint32_t)nwarps * 32u) {
+      for (uint32_t j0 = (uint32_t)widx * 32u; j0 < cnt; j0 += (uint32_t)nper * 32u) {
         uint32_t j = j0 + lane;
         uint32_t row = PBX_NO_ROW;
         if (j < cnt) {
@@ -323,15 +339,54 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
   PBX_TS(10);
 
   // ---- Q2: ship merged records to their owners
-  for (int o = 0; o < R; ++o) {
-    if (o == c.rank) continue;  // records for the local shard are applied straight from push_acc
-    const int64_t items = (int64_t)c.send_cnt[o] * pchunks;
-    const float4* src = reinterpret_cast<const float4*>(c.push_acc + (uint64_t)o * cap * PD);
-    float4* dst = reinterpret_cast<float4*>(c.push_mail[o] + (uint64_t)c.rank * cap * PD);  // remote
-    for (int64_t it = gtid; it < items; it += gstride) dst[it] = src[it];
+  // (records for the local shard are applied straight from push_acc).  The CTAs are split over
+  // the R-1 remote owners — block lb ships to owner (rank + 1 + lb % (R-1)) % R — so every pair of
+  // GPUs exchanges at the same rate instead of all ranks hitting owner 0 first.
+  if (R > 1) {
+    const int nd = R - 1;
+    const int di = bpr >= nd ? lb % nd : 0;
+    const int bl = bpr >= nd ? lb / nd : lb;
+    const int nb = bpr >= nd ? (bpr - di + nd - 1) / nd : bpr;
+    for (int rep = 0; rep < (bpr >= nd ? 1 : nd); ++rep) {
+      const int o = (c.rank + 1 + di + rep) % R;
+      const int64_t items = (int64_t)c.send_cnt[o] * pchunks;
+      const float4* src = reinterpret_cast<const float4*>(c.push_acc + (uint64_t)o * cap * PD);
+      float4* dst = reinterpret_cast<float4*>(c.push_mail[o] + (uint64_t)c.rank * cap * PD);  // remote
+      for (int64_t it = (int64_t)bl * PBX_PUSH_THREADS + tid; it < items; it += (int64_t)nb * PBX_PUSH_THREADS)
+        dst[it] = src[it];
+    }
   }
   xbarrier<EMU>(grid, c, e0 + 1, lb == 0);
   PBX_TS(11);
+
+  // ---- folded dense allreduce (one-shot per slice over peer memory, scale fused)
+  if (a.dense_ctx) {
+    const PbxSymmDev& d = *a.dense_ctx;
+    const int64_t n = a.dense_n, off = a.dense_off;
+    const int64_t chunk = ((n + R - 1) / R + 3) / 4 * 4;
+    const int64_t b = min(n, (int64_t)d.rank * chunk), e = min(n, b + chunk);
+    const int64_t nv = (e - b) / 4;
+    for (int64_t i = gtid; i < nv; i += gstride) {
+      const int64_t idx = off + b + i * 4;
+      float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+      for (int p = 0; p < PBX_MAX_RANKS; ++p)
+        if (p < R) {
+          const float4 v = __ldcg(reinterpret_cast<const float4*>(d.data[(d.rank + p) % R] + idx));
+          acc.x += v.x; acc.y += v.y; acc.z += v.z; acc.w += v.w;
+        }
+      acc.x *= a.dense_scale; acc.y *= a.dense_scale; acc.z *= a.dense_scale; acc.w *= a.dense_scale;
+#pragma unroll
+      for (int p = 0; p < PBX_MAX_RANKS; ++p)
+        if (p < R) *reinterpret_cast<float4*>(d.data[(d.rank + p) % R] + idx) = acc;
+    }
+    for (int64_t i = b + nv * 4 + gtid; i < e; i += gstride) {
+      float acc = 0.f;
+      for (int p = 0; p < R; ++p) acc += __ldcg(d.data[p] + off + i);
+      acc *= a.dense_scale;
+      for (int p = 0; p < R; ++p) d.data[p][off + i] = acc;
+    }
+  }
 
   // ---- Q3: owner applies the fused sparse optimizer.
   // Rows of one 128-byte line (every optimizer): WARP TILES over the flattened list of all
@@ -518,7 +573,12 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
     }
   }
   PBX_TS(12);
-  if (lb == 0 && tid == 0) *c.epoch = e0 + 1;
+  if (a.dense_ctx) {
+    xbarrier<EMU>(grid, c, e0 + 2, lb == 0);   // every peer's reduced slices have landed
+    if (lb == 0 && tid == 0) *c.epoch = e0 + 2;
+  } else {
+    if (lb == 0 && tid == 0) *c.epoch = e0 + 1;
+  }
 }
 
 }  // namespace
@@ -783,6 +843,10 @@ int pbx_sparse_push_ex(void* hnd, const uint32_t* d_restore, int64_t n, const fl
                        const float* d_cvm, const int32_t* d_lod, int B, int S, int Eo, int cvm_offset, int dim_off,
                        const float* d_gkeys, const int32_t* d_key2slot, int hidden, int mode, float grad_scale,
                        cudaStream_t st);
+int pbx_sparse_push_dense(void* hnd, const uint32_t* d_restore, int64_t n, const float* d_dout, int ld_dout,
+                          const float* d_cvm, const int32_t* d_lod, int B, int S, int Eo, int cvm_offset, int dim_off,
+                          const float* d_gkeys, const int32_t* d_key2slot, int hidden, int mode, float grad_scale,
+                          void* symm, int64_t dense_off, int64_t dense_n, float dense_scale, cudaStream_t st);
 int pbx_sparse_push(void* hnd, const uint32_t* d_restore, int64_t n, const float* d_dout, const float* d_cvm,
                     const int32_t* d_lod, int B, int S, int Eo, int cvm_offset, int dim_off, const float* d_gkeys,
                     const int32_t* d_key2slot, int hidden, int mode, float grad_scale, cudaStream_t st) {
@@ -795,6 +859,18 @@ int pbx_sparse_push_ex(void* hnd, const uint32_t* d_restore, int64_t n, const fl
                        const float* d_cvm, const int32_t* d_lod, int B, int S, int Eo, int cvm_offset, int dim_off,
                        const float* d_gkeys, const int32_t* d_key2slot, int hidden, int mode, float grad_scale,
                        cudaStream_t st) {
+  return pbx_sparse_push_dense(hnd, d_restore, n, d_dout, ld_dout, d_cvm, d_lod, B, S, Eo, cvm_offset, dim_off, d_gkeys,
+                               d_key2slot, hidden, mode, grad_scale, nullptr, 0, 0, 1.f, st);
+}
+
+// The same with the data-parallel dense-gradient allreduce folded in: `symm` is a pbx_symm handle
+// whose region holds the flat gradient buffer at [dense_off, dense_off + dense_n) floats on every
+// rank (same group, same rank numbering as the sparse engine); on return of the kernel that range
+// holds sum over ranks * dense_scale on every rank.  symm == NULL: plain push.
+int pbx_sparse_push_dense(void* hnd, const uint32_t* d_restore, int64_t n, const float* d_dout, int ld_dout,
+                          const float* d_cvm, const int32_t* d_lod, int B, int S, int Eo, int cvm_offset, int dim_off,
+                          const float* d_gkeys, const int32_t* d_key2slot, int hidden, int mode, float grad_scale,
+                          void* symm, int64_t dense_off, int64_t dense_n, float dense_scale, cudaStream_t st) {
   PbxSparseCtx* c = (PbxSparseCtx*)hnd;
   if (mode == 0) PBX_REQUIRE(ld_dout >= S * Eo, "ld_dout %d < S*Eo %d", ld_dout, S * Eo);
   PBX_REQUIRE(c->h.table.L.embedx_dim <= 256, "embedx_dim > 256 not supported by the push kernel");
@@ -810,6 +886,21 @@ int pbx_sparse_push_ex(void* hnd, const uint32_t* d_restore, int64_t n, const fl
   pbx_fill_push_args(args.a[0], d_restore, n, d_dout, d_cvm, d_lod, B, S, Eo, cvm_offset, dim_off, d_gkeys,
                      d_key2slot, hidden, mode, grad_scale);
   if (mode == 0) args.a[0].ld_dout = ld_dout;
+  if (symm && c->h.nranks > 1) {
+    PbxSymm* sm = (PbxSymm*)symm;
+    PBX_REQUIRE(sm->h.nranks == c->h.nranks && sm->h.rank == c->h.rank, "push: symm group differs from the sparse group");
+    PBX_REQUIRE((dense_off & 3) == 0 && (uint64_t)(dense_off + dense_n) * 4 <= sm->bytes - sm->data_off,
+                "push: dense range outside the symmetric region");
+    if (sm->dirty) {
+      PBX_CUDA_CHECK(cudaMemcpyAsync(sm->d, &sm->h, sizeof(PbxSymmDev), cudaMemcpyHostToDevice, st));
+      PBX_CUDA_CHECK(cudaStreamSynchronize(st));
+      sm->dirty = false;
+    }
+    args.a[0].dense_ctx = sm->d;
+    args.a[0].dense_off = dense_off;
+    args.a[0].dense_n = dense_n;
+    args.a[0].dense_scale = dense_scale;
+  }
   const PbxSparseDev* dctx = c->d;
   int nvr = 1;
   void* kargs[] = {(void*)&dctx, (void*)&nvr, (void*)&args};

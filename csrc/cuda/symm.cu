@@ -17,23 +17,7 @@
 #include <vector>
 namespace cg = cooperative_groups;
 
-struct PbxSymmDev {
-  int rank, nranks;
-  uint64_t* flags[PBX_MAX_RANKS];  // [64] per rank
-  float* data[PBX_MAX_RANKS];      // user region per rank
-  uint64_t* epoch;
-  int* status;
-};
-
-struct PbxSymm {
-  PbxSymmDev h;
-  PbxSymmDev* d;
-  bool dirty;
-  void* base;
-  size_t bytes, data_off;
-  void* peer_base[PBX_MAX_RANKS];
-  bool opened[PBX_MAX_RANKS];
-};
+#include "symm.cuh"
 
 namespace {
 

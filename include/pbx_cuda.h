@@ -69,6 +69,15 @@ int pbx_sparse_push_ex(void* ctx, const uint32_t* d_restore, int64_t n, const fl
                        const float* d_cvm, const int32_t* d_lod, int B, int S, int Eo, int cvm_offset, int dim_off,
                        const float* d_gkeys, const int32_t* d_key2slot, int hidden, int mode, float grad_scale,
                        pbx_stream_t stream);
+/* push_ex with the data-parallel dense-gradient allreduce folded into the kernel's own barriers:
+ * `symm` (a pbx_symm handle of the same group) holds the flat gradient buffer at
+ * [dense_off, dense_off + dense_n) floats; afterwards that range is sum over ranks * dense_scale
+ * on every rank.  symm == NULL: plain push. */
+int pbx_sparse_push_dense(void* ctx, const uint32_t* d_restore, int64_t n, const float* d_dout, int ld_dout,
+                          const float* d_cvm, const int32_t* d_lod, int B, int S, int Eo, int cvm_offset,
+                          int dim_off, const float* d_gkeys, const int32_t* d_key2slot, int hidden, int mode,
+                          float grad_scale, void* symm, int64_t dense_off, int64_t dense_n, float dense_scale,
+                          pbx_stream_t stream);
 int pbx_sparse_pull_emu(void* const* ctxs, int nranks, const uint64_t* const* d_keys, const int64_t* n,
                         uint32_t* const* d_restore, pbx_stream_t stream);
 int pbx_sparse_push_emu(void* const* ctxs, int nranks, const uint32_t* const* d_restore, const int64_t* n,

@@ -199,11 +199,25 @@ class DenseSync:
         self.store, self.opt, self.mode, self.k = store, opt, mode, max(1, sync_weight_step)
         self.async_table = async_table
         self.steps = 0
+        self.fold_engine = None
         if mode == "async":
             from ..host import AsyncDenseTable
             self.async_table = async_table or AsyncDenseTable(store.numel, lr=opt.lr)
             if store.rank == 0 or async_table is None:
                 self.async_table.set_params(store.flat)
+
+    def fold_into(self, engine) -> bool:
+        """Let the sparse engine's push kernel carry the per-step gradient allreduce (it runs after
+        every dense gradient of the step is final; see csrc/cuda/sparse_a2a.cu).  Only for the
+        plain allreduce mode over symmetric memory with the same ranks as the sparse group."""
+        s = self.store
+        if (self.mode != "allreduce" or not s.use_symm or engine is None or not FLAGS.pbx_fold_dense_allreduce
+                or getattr(engine, "nranks", 1) != s.nranks):
+            return False
+        engine.fold_dense = (s.symm, 0, s.numel, 1.0 / s.nranks)
+        engine.fold_done = False
+        self.fold_engine = engine
+        return True
 
     def before_forward(self) -> None:
         if self.mode == "async":
@@ -217,7 +231,11 @@ class DenseSync:
         if self.mode == "none":
             o.step()
         elif self.mode == "allreduce":
-            s.allreduce_grads()
+            eng = self.fold_engine
+            if eng is not None and getattr(eng, "fold_done", False):
+                eng.fold_done = False          # the sparse push of this step already reduced the grads
+            else:
+                s.allreduce_grads()
             o.step()
         elif self.mode == "kstep":
             o.step()

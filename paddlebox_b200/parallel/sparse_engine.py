@@ -103,6 +103,17 @@ class SparseEngine:
         ld = dout.stride(0) if ld_dout is None else ld_dout
         assert dout.stride(1) == 1 and dout.shape[0] == B and dout.shape[1] >= S * Eo and ld >= S * Eo \
             and dout.dtype == torch.float32
+        fold = getattr(self, "fold_dense", None)
+        if fold is not None and self.nranks > 1:
+            # the trainer's dense-gradient allreduce rides on this kernel's barriers
+            symm, off, n, scale = fold
+            N.check(N.cuda().pbx_sparse_push_dense(self._h, N.ptr(restore), C.c_int64(restore.numel()), N.ptr(dout), ld,
+                                                   N.ptr(cvm), N.ptr(lod), B, S, Eo, cvm_offset, dim_off, None, None,
+                                                   0, 0, C.c_float(grad_scale), symm._h, C.c_int64(off),
+                                                   C.c_int64(n), C.c_float(scale), N.stream_ptr()),
+                    "pbx_sparse_push_dense")
+            self.fold_done = True
+            return
         N.check(N.cuda().pbx_sparse_push_ex(self._h, N.ptr(restore), C.c_int64(restore.numel()), N.ptr(dout), ld,
                                             N.ptr(cvm), N.ptr(lod), B, S, Eo, cvm_offset, dim_off, None, None, 0,
                                             0, C.c_float(grad_scale), N.stream_ptr()), "pbx_sparse_push")

@@ -55,6 +55,8 @@ class CTRTrainer:
         self.store = DenseParamStore(model, self.rank, self.world, group)
         self.opt = DenseOptimizer(self.store, lr=self.cfg.dense_lr, kind=self.cfg.dense_optimizer)
         self.sync = DenseSync(self.store, self.opt, mode, self.cfg.sync_weight_step)
+        if self.world > 1 and not self.cfg.is_test:
+            self.sync.fold_into(getattr(self.box, "engine", None))
         if self.world > 1:
             self.store.broadcast_params(0)
             self.store.mark_dirty()
