@@ -73,26 +73,40 @@ namespace {
 template <bool EMU>
 __device__ __forceinline__ void xbarrier(cg::grid_group& grid, const PbxSparseDev& c, uint64_t target,
                                          bool leader_block) {
-  // Every thread's (possibly remote) stores are ordered before the grid barrier at gpu scope;
-  // the signalling threads then issue ONE system-scope fence before publishing the flag, which by
-  // cumulativity makes all of them visible to the peer that acquires the flag.  (A system fence
-  // in every thread costs an ERRBAR per thread and showed up as ~15% of the kernel in ncu.)
-  grid.sync();
-  if (!EMU && c.nranks > 1) {
-    if (leader_block && threadIdx.x < c.nranks) {
-      int p = threadIdx.x;
+  // Cross-rank barrier and local grid barrier in ONE level (real multi-rank runs):
+  //   arrive : every CTA orders its (possibly remote) stores at gpu scope and bumps a counter;
+  //            the LAST CTA of the rank issues one system-scope fence and publishes `target` into
+  //            every peer's flag array (and its own) — by cumulativity all CTAs' stores are
+  //            visible to whoever acquires the flag.  (A system fence in every thread costs an
+  //            ERRBAR per thread and showed up as ~15% of the kernel in ncu.)
+  //   wait   : R threads of EVERY CTA poll the local flag array; no second grid barrier, no
+  //            leader hop.  The own-rank flag doubles as the local grid barrier.
+  if (EMU || c.nranks == 1) {
+    grid.sync();
+    return;
+  }
+  (void)leader_block;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    unsigned long long* cnt = reinterpret_cast<unsigned long long*>(c.epoch + 2);
+    const unsigned long long old = atomicAdd(cnt, 1ull);
+    if (old + 1ull == (unsigned long long)gridDim.x) {
+      *cnt = 0ull;                              // nobody re-arrives before seeing the flags below
       __threadfence_system();
-      pbx_st_release_sys(c.flags[p] + c.rank, target);
-      uint64_t t0 = pbx_globaltimer();
-      while (pbx_ld_acquire_sys(c.flags[c.rank] + p) < target) {
-        if (pbx_globaltimer() - t0 > 20000000000ull) {  // 20 s: a peer died; fail loudly, do not hang
-          atomicExch(c.status, 2);
-          break;
-        }
+      for (int p = 0; p < c.nranks; ++p) pbx_st_release_sys(c.flags[p] + c.rank, target);
+    }
+  }
+  if (threadIdx.x < c.nranks) {
+    const uint64_t t0 = pbx_globaltimer();
+    while (pbx_ld_acquire_sys(c.flags[c.rank] + threadIdx.x) < target) {
+      if (pbx_globaltimer() - t0 > 20000000000ull) {  // 20 s: a peer died; fail loudly, do not hang
+        atomicExch(c.status, 2);
+        break;
       }
     }
-    grid.sync();
   }
+  __syncthreads();
 }
 
 template <bool EMU>
@@ -352,8 +366,17 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
       const int64_t items = (int64_t)c.send_cnt[o] * pchunks;
       const float4* src = reinterpret_cast<const float4*>(c.push_acc + (uint64_t)o * cap * PD);
       float4* dst = reinterpret_cast<float4*>(c.push_mail[o] + (uint64_t)c.rank * cap * PD);  // remote
-      for (int64_t it = (int64_t)bl * PBX_PUSH_THREADS + tid; it < items; it += (int64_t)nb * PBX_PUSH_THREADS)
-        dst[it] = src[it];
+      // four independent 16-byte moves per thread in flight (local L2 read -> NVLink store)
+      const int64_t step = (int64_t)nb * PBX_PUSH_THREADS;
+      for (int64_t it = (int64_t)bl * PBX_PUSH_THREADS + tid; it < items; it += 4 * step) {
+        float4 v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (it + u * step < items) v[u] = __ldcg(src + it + u * step);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (it + u * step < items) dst[it + u * step] = v[u];
+      }
     }
   }
   xbarrier<EMU>(grid, c, e0 + 1, lb == 0);

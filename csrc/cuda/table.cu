@@ -45,7 +45,8 @@ __global__ void k_insert(PbxTableView t, const uint64_t* __restrict__ keys, int6
     if (rows) {
       if (fresh) {
         const float* src = rows + i * S;
-        for (int j = 0; j < S; ++j) row[j] = src[j];
+        for (int j = 0; j < S - 1; ++j) row[j] = src[j];
+        row[S - 1] = 0.f;   // the lock / requester-count word is per-pass state, never loaded
       }
     } else if (fresh) {
       pbx_row_init(t, row, key);
@@ -117,7 +118,8 @@ __global__ void k_dump(PbxTableView t, uint64_t* out_keys, float* out_rows, unsi
       if (out_rows) {
         const float* row = t.vals + i * S;
         float* dst = out_rows + pos * S;
-        for (int j = 0; j < S; ++j) dst[j] = row[j];
+        for (int j = 0; j < S - 1; ++j) dst[j] = row[j];
+        dst[S - 1] = 0.f;   // lock / requester-count word: not part of the value
       }
     }
     if (clear_dirty) t.dirty[i] = 0;
