@@ -110,6 +110,28 @@ def bench_big_tiles(out):
         print({"case": name, "cublas_us": round(us, 1), "cublas_tflops": round(2.0 * M * Nn * K / us / 1e6, 1)}, flush=True)
 
 
+def bench_fwd_sweep(out, flush):
+    """forward / dgrad shapes of the DeepFM tower: tile width sweep (run under PBX_GEMM_PIPE=deep|shallow)."""
+    from paddlebox_b200.ops.mlp import _pad8, gemm_bf16_tn
+    dev = torch.device("cuda")
+    pipe = os.environ.get("PBX_GEMM_PIPE", "auto")
+    for name, M, Nn, K in [("fwd L0", 4096, 512, 507), ("fwd L1", 4096, 256, 512), ("fwd L2", 4096, 128, 256),
+                           ("dgrad L1", 4096, 512, 256), ("dgrad L2", 4096, 256, 128)]:
+        A = torch.randn(M, _pad8(K), device=dev).to(torch.bfloat16)
+        B = torch.randn(Nn, _pad8(K), device=dev).to(torch.bfloat16)
+        ob = torch.zeros(M, _pad8(Nn), dtype=torch.bfloat16, device=dev)
+        ot = torch.zeros(Nn, _pad8(M), dtype=torch.bfloat16, device=dev)
+        bias = torch.zeros(Nn, device=dev)
+        for bn in (32, 64, 128):
+            if bn > Nn:
+                continue
+            us = timeit(lambda: gemm_bf16_tn(A, B, M, Nn, K, bias=bias, out_bf16=ob, out_t=ot, relu=True, block_n=bn),
+                        flush=flush)
+            out.append({"kernel": "gemm_fwd_sweep", "pipe": pipe, "case": name, "bn": bn,
+                        "ctas": ((M + 127) // 128) * ((Nn + bn - 1) // bn), "us": round(us, 2)})
+            print(out[-1], flush=True)
+
+
 def bench_wgrad_sweep(out, flush):
     """wgrad shapes of the DeepFM tower: tile width x split-K sweep (atomics contention vs main-loop length)."""
     from paddlebox_b200.ops.mlp import _pad8, gemm_bf16_tn
@@ -220,6 +242,8 @@ def main():
         bench_gemm(out, flush)
     if "big_tiles" in a.what:
         bench_big_tiles(out)
+    if "fwd_sweep" in a.what:
+        bench_fwd_sweep(out, flush)
     if "wgrad_sweep" in a.what:
         bench_wgrad_sweep(out, flush)
     if "sparse" in a.what:

@@ -17,6 +17,7 @@
 // batch_fc_op.cu:243) — there is no tensor-core code in the reference.
 #include "common.cuh"
 #include "pbx_types.h"
+#include <cstdlib>
 #include <cuda.h>
 #include <cudaTypedefs.h>
 
@@ -131,14 +132,16 @@ __host__ __device__ constexpr uint32_t make_idesc(int m, int n) {
   return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
 
-template <int BN>
+template <int BN, int STG = 0>
 struct SmemLayout {
   static constexpr int A_BYTES = BM * BK * 2;
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   // deep pipelines: the MLP-tower GEMMs have 4-8 k-blocks and start cold, so every k-block that
   // is in flight at once removes one exposed DRAM round trip from the main loop
-  static constexpr int STAGES = (196 * 1024 / STAGE_BYTES) > 8 ? 8 : (196 * 1024 / STAGE_BYTES);
+  // STG = 0: as deep as 196 KB allows (one CTA per SM); STG > 0: that many stages (the grouped
+  // kernel uses ~96 KB so that two CTAs share an SM and one's epilogue overlaps the other's loads)
+  static constexpr int STAGES = STG > 0 ? STG : ((196 * 1024 / STAGE_BYTES) > 8 ? 8 : (196 * 1024 / STAGE_BYTES));
   static constexpr int BAR_BYTES = 256;
   static constexpr int TOTAL = STAGES * STAGE_BYTES + 1024 /*align slack*/ + BAR_BYTES + BN * 4 /*bias*/;
   // the epilogue reuses the stage memory for a row-major and a transposed bf16 staging tile
@@ -146,11 +149,11 @@ struct SmemLayout {
 };
 
 // One output tile (bx, by) of split bz of one GEMM problem; the whole CTA participates.
-template <int BN>
+template <int BN, int STG = 0>
 __device__ __forceinline__ void gemm_tile(const CUtensorMap* pmap_a, const CUtensorMap* pmap_b, int M, int N, int K,
                                           int kb_per_split, const GemmEpilogue& ep, int bx, int by, int bz) {
   extern __shared__ uint8_t smem_raw[];
-  using L = SmemLayout<BN>;
+  using L = SmemLayout<BN, STG>;
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   constexpr int STAGES = L::STAGES;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + STAGES * L::STAGE_BYTES);
@@ -439,11 +442,11 @@ __device__ __forceinline__ void gemm_tile(const CUtensorMap* pmap_a, const CUten
   if (threadIdx.x == 0) GEMM_TS(7);
 }
 
-template <int BN>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+template <int BN, int STG>
+__global__ void __launch_bounds__(GEMM_THREADS, STG > 0 ? 2 : 1)
 k_gemm_tcgen05(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, int M, int N,
                int K, int kb_per_split, GemmEpilogue ep) {
-  gemm_tile<BN>(&map_a, &map_b, M, N, K, kb_per_split, ep, blockIdx.x, blockIdx.y, blockIdx.z);
+  gemm_tile<BN, STG>(&map_a, &map_b, M, N, K, kb_per_split, ep, blockIdx.x, blockIdx.y, blockIdx.z);
 }
 
 // Several independent GEMM problems in ONE launch (all weight gradients of a tower; the experts of
@@ -461,7 +464,10 @@ struct GroupedGemm {
 };
 
 template <int BN>
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+struct GroupedStages { static constexpr int value = BN >= 128 ? 3 : 4; };
+
+template <int BN>
+__global__ void __launch_bounds__(GEMM_THREADS, 2)
 k_gemm_tcgen05_grouped(const __grid_constant__ GroupedGemm g) {
   int p = 0;
   while (p < g.n - 1 && (int)blockIdx.x >= g.cta_end[p]) ++p;
@@ -469,7 +475,8 @@ k_gemm_tcgen05_grouped(const __grid_constant__ GroupedGemm g) {
   const int bx = local % g.gx[p];
   const int by = (local / g.gx[p]) % g.gy[p];
   const int bz = local / (g.gx[p] * g.gy[p]);
-  gemm_tile<BN>(&g.map_a[p], &g.map_b[p], g.M[p], g.N[p], g.K[p], g.kb_per[p], g.ep[p], bx, by, bz);
+  gemm_tile<BN, GroupedStages<BN>::value>(&g.map_a[p], &g.map_b[p], g.M[p], g.N[p], g.K[p], g.kb_per[p], g.ep[p], bx, by,
+                                      bz);
 }
 
 // --------- plain SIMT kernel with the same contract: numerics cross-check / fallback ---------
@@ -529,7 +536,9 @@ int make_map(CUtensorMap* map, const void* base, int rows, int cols, int ld, int
   return 0;
 }
 
-template <int BN>
+// STG = 0: deep pipeline, one CTA per SM (grids of at most one wave: latency matters);
+// STG > 0: ~96 KB pipeline, two CTAs per SM (multi-wave grids: one CTA's epilogue overlaps the other's loads)
+template <int BN, int STG>
 int launch_tc(const __nv_bfloat16* A, int lda, const __nv_bfloat16* B, int ldb, int M, int N, int K, int splitk,
               const GemmEpilogue& ep, cudaStream_t st) {
   CUtensorMap ma, mb;
@@ -544,12 +553,12 @@ int launch_tc(const __nv_bfloat16* A, int lda, const __nv_bfloat16* B, int ldb, 
   splitk = (num_kb + kb_per - 1) / kb_per;
   static bool attr_set = false;
   if (!attr_set) {
-    PBX_CUDA_CHECK(cudaFuncSetAttribute(k_gemm_tcgen05<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        SmemLayout<BN>::TOTAL));
+    PBX_CUDA_CHECK(cudaFuncSetAttribute(k_gemm_tcgen05<BN, STG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                        SmemLayout<BN, STG>::TOTAL));
     attr_set = true;
   }
   dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, splitk);
-  k_gemm_tcgen05<BN><<<grid, GEMM_THREADS, SmemLayout<BN>::TOTAL, st>>>(ma, mb, M, N, K, kb_per, ep);
+  k_gemm_tcgen05<BN, STG><<<grid, GEMM_THREADS, SmemLayout<BN, STG>::TOTAL, st>>>(ma, mb, M, N, K, kb_per, ep);
   PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
@@ -592,10 +601,10 @@ int launch_grouped(const PbxGemmProblem* pr, int n, cudaStream_t st) {
   static bool attr_set = false;
   if (!attr_set) {
     PBX_CUDA_CHECK(cudaFuncSetAttribute(k_gemm_tcgen05_grouped<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                        SmemLayout<BN>::TOTAL));
+                                        SmemLayout<BN, GroupedStages<BN>::value>::TOTAL));
     attr_set = true;
   }
-  k_gemm_tcgen05_grouped<BN><<<ctas, GEMM_THREADS, SmemLayout<BN>::TOTAL, st>>>(g);
+  k_gemm_tcgen05_grouped<BN><<<ctas, GEMM_THREADS, SmemLayout<BN, GroupedStages<BN>::value>::TOTAL, st>>>(g);
   PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
@@ -672,7 +681,10 @@ int pbx_gemm_bf16_tn(const void* A, int lda, const void* B, int ldb, int M, int 
   if (block_n == 0) {
     // enough CTAs to cover the 148 SMs when the problem allows it
     long long tiles128 = (long long)((M + BM - 1) / BM) * ((N + 127) / 128) * (splitk > 0 ? splitk : 1);
-    block_n = (N <= 32) ? 32 : (N <= 64 || tiles128 < 96) ? 64 : 128;
+    // up to one wave of 128-wide tiles: 64-wide tiles instead (twice the CTAs, two per SM with the
+    // shallow pipeline, so one CTA's epilogue overlaps the other's loads: 12.3 vs 14.3 us on the
+    // 4096x512x507 layer)
+    block_n = (N <= 32) ? 32 : (N <= 64 || tiles128 <= 148) ? 64 : 128;
     // large problems: 128x256 tiles halve the A-operand traffic per FLOP (measured 0.80 of the
     // cuBLAS-measured peak at 8192^3 vs 0.51 with 128x128) once there are >= 2 waves of them
     long long tiles256 = (long long)((M + BM - 1) / BM) * ((N + 255) / 256) * (splitk > 0 ? splitk : 1);
@@ -680,11 +692,19 @@ int pbx_gemm_bf16_tn(const void* A, int lda, const void* B, int ldb, int M, int 
   }
   const __nv_bfloat16* a = (const __nv_bfloat16*)A;
   const __nv_bfloat16* b = (const __nv_bfloat16*)B;
+  // more CTAs than SMs: the shallow two-CTAs-per-SM variant (PBX_GEMM_PIPE=deep|shallow overrides)
+  static const char* pipe_env = getenv("PBX_GEMM_PIPE");
+  const long long ctas = (long long)((M + BM - 1) / BM) * ((N + block_n - 1) / block_n) * (splitk > 0 ? splitk : 1);
+  bool shallow = ctas > 148;
+  if (pipe_env) shallow = pipe_env[0] == 's';
   switch (block_n) {
-    case 32: return launch_tc<32>(a, lda, b, ldb, M, N, K, splitk, ep, st);
-    case 64: return launch_tc<64>(a, lda, b, ldb, M, N, K, splitk, ep, st);
-    case 128: return launch_tc<128>(a, lda, b, ldb, M, N, K, splitk, ep, st);
-    case 256: return launch_tc<256>(a, lda, b, ldb, M, N, K, splitk, ep, st);
+    case 32: return shallow ? launch_tc<32, 4>(a, lda, b, ldb, M, N, K, splitk, ep, st)
+                            : launch_tc<32, 0>(a, lda, b, ldb, M, N, K, splitk, ep, st);
+    case 64: return shallow ? launch_tc<64, 4>(a, lda, b, ldb, M, N, K, splitk, ep, st)
+                            : launch_tc<64, 0>(a, lda, b, ldb, M, N, K, splitk, ep, st);
+    case 128: return shallow ? launch_tc<128, 3>(a, lda, b, ldb, M, N, K, splitk, ep, st)
+                             : launch_tc<128, 0>(a, lda, b, ldb, M, N, K, splitk, ep, st);
+    case 256: return launch_tc<256, 0>(a, lda, b, ldb, M, N, K, splitk, ep, st);
     default: PBX_REQUIRE(false, "gemm: unsupported block_n %d", block_n);
   }
   return 0;

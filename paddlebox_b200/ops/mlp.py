@@ -278,7 +278,7 @@ class FusedMLP(nn.Module):
             if b.grad is None:
                 b.grad = torch.zeros_like(b.data)
             # wgrad: dW[N, K] += dZ^T[N, B] . (H^T[K, B])^T   (split-K over the batch)
-            splitk = max(1, min(16, B // 512))
+            splitk = max(1, min(16, B // 1024))     # two CTAs per SM in the grouped launch: one wave
             # (the ones row of Ht makes output column K the bias gradient: no separate column-sum pass)
             # Weight gradients are off the critical path of the dgrad chain: they are collected
             # and issued as ONE grouped launch once every dZ exists.
@@ -295,7 +295,9 @@ class FusedMLP(nn.Module):
                 gemm_bf16_tn(ws.dZ[l], self._wbt[l], B, K, Nn, mask=ws.H[l], out_bf16=ws.dZ[l - 1],
                              out_t=ws.dZt[l - 1])
             elif need_dx:
-                dx = torch.empty(B, K, dtype=torch.float32, device=dout.device)
+                # row stride padded to 16 bytes: the epilogue then writes 16-byte vectors (with an
+                # odd stride it falls back to 4-byte stores that touch 32 rows per instruction)
+                dx = torch.empty(B, (K + 3) // 4 * 4, dtype=torch.float32, device=dout.device)[:, :K]
                 gemm_bf16_tn(ws.dZ[0], self._wbt[0], B, K, Nn, out_f32=dx)
         if not wgrads:
             pass
