@@ -13,7 +13,7 @@ namespace cg = cooperative_groups;
 
 namespace {
 
-constexpr int BB_THREADS = 512;
+constexpr int BB_THREADS = 1024;
 
 __device__ __forceinline__ int bag_len(const int32_t* ro, int S, int B, int g) {
   const int s = g / B, b = g % B;
@@ -58,12 +58,23 @@ k_batch_build(const uint64_t* __restrict__ rec_keys, const int32_t* __restrict__
   __shared__ int s_total;
   __shared__ int s_carry;
 
-  // phase 1: per-block total length
-  int local = 0;
-  for (int g = g0 + threadIdx.x; g < g1; g += BB_THREADS) local += bag_len(rec_off, S, B, g);
-  int dummy = block_exscan(local, &s_total);
-  (void)dummy;
-  if (threadIdx.x == 0) block_sums[blockIdx.x] = s_total;
+  // phase 1: per-block total length.  When a block's share fits one bag per thread (the usual
+  // case: G <= blocks * 1024) the lengths and their in-block prefix stay in registers and phase 3
+  // neither re-reads the offsets nor scans again.
+  const bool single = per_block <= BB_THREADS;
+  int len0 = 0, ex0 = 0;
+  if (single) {
+    const int g = g0 + threadIdx.x;
+    len0 = g < g1 ? bag_len(rec_off, S, B, g) : 0;
+    ex0 = block_exscan(len0, &s_total);
+  } else {
+    int local = 0;
+    for (int g = g0 + threadIdx.x; g < g1; g += BB_THREADS) local += bag_len(rec_off, S, B, g);
+    int dummy = block_exscan(local, &s_total);
+    (void)dummy;
+  }
+  const int my_total = s_total;
+  if (threadIdx.x == 0) block_sums[blockIdx.x] = my_total;
   grid.sync();
 
   // phase 2: every block derives its base from the (few) block sums
@@ -74,7 +85,19 @@ k_batch_build(const uint64_t* __restrict__ rec_keys, const int32_t* __restrict__
   if (threadIdx.x == 0) s_carry = s_total;
   __syncthreads();
 
-  // phase 3: chunked scan inside the block -> lod, then scatter keys
+  // phase 3: lod + key scatter
+  if (single) {
+    const int g = g0 + threadIdx.x;
+    const int start = s_carry + ex0;
+    if (g < g1) {
+      lod_out[g] = start;
+      const int s = g / B, b = g % B;
+      const int32_t src = rec_off[(int64_t)b * (S + 1) + s];
+      for (int j = 0; j < len0; ++j) keys_out[start + j] = rec_keys[src + j];
+    }
+    if (blockIdx.x == gridDim.x - 1 && threadIdx.x == 0) lod_out[G] = s_carry + my_total;
+    return;
+  }
   for (int c0 = g0; c0 < g1; c0 += BB_THREADS) {
     const int g = c0 + threadIdx.x;
     const int len = g < g1 ? bag_len(rec_off, S, B, g) : 0;
@@ -103,7 +126,7 @@ int pbx_batch_build(const uint64_t* d_rec_keys, const int32_t* d_rec_off, int B,
                     int32_t* d_lod_out, int32_t* d_scratch, cudaStream_t st) {
   if (B <= 0 || S <= 0) return 0;
   int G = S * B;
-  int blocks = (G + BB_THREADS * 4 - 1) / (BB_THREADS * 4);
+  int blocks = (G + BB_THREADS - 1) / BB_THREADS;   // one bag per thread while the SMs last
   int sms = pbx_num_sms();
   if (blocks > sms) blocks = sms;
   if (blocks < 1) blocks = 1;
@@ -137,7 +160,7 @@ int pbx_batch_build(const uint64_t* d_rec_keys, const int32_t* d_rec_off, int B,
 // somewhere unrelated).  The real device address is obtained once per device with
 // cudaGetSymbolAddress() while that device is current, and that address is what the kernel gets.
 #define PBX_BB_STATIC_SCRATCH_INTS 512                       /* 2 KiB */
-#define PBX_BB_STATIC_BAGS_PER_BLOCK (BB_THREADS * 4)         /* same blocking as pbx_batch_build */
+#define PBX_BB_STATIC_BAGS_PER_BLOCK 2048                    /* bags per thread block (before the SM-count cap) */
 #define PBX_BB_STATIC_MAX_BAGS ((long long)PBX_BB_STATIC_SCRATCH_INTS * PBX_BB_STATIC_BAGS_PER_BLOCK)
 
 static __device__ __align__(256) int32_t g_bb_static_scratch[PBX_BB_STATIC_SCRATCH_INTS];
