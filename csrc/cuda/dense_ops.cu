@@ -217,7 +217,7 @@ k_ctr_head_fwd(const float* __restrict__ tower, int ld_tower, const float* __res
 __global__ void __launch_bounds__(1024)
 k_ctr_head_bwd(const float* __restrict__ dlogit, const float* __restrict__ gloss, int B,
                float* __restrict__ d_tower, float* __restrict__ d_extra, float* __restrict__ d_bias,
-               int accumulate) {
+               int accumulate, __nv_bfloat16* __restrict__ dz, int ld_dz, __nv_bfloat16* __restrict__ dzt) {
   __shared__ float red[32];
   const float g = gloss[0];
   float local = 0.f;
@@ -234,6 +234,11 @@ k_ctr_head_bwd(const float* __restrict__ dlogit, const float* __restrict__ gloss
       if (i >= B) break;
       if (d_tower) d_tower[i] = dv[u];
       if (d_extra) d_extra[i] = dv[u];
+      if (dz) {            // bf16 operands of the tower's last-layer backward GEMMs, written in place
+        const __nv_bfloat16 h = __float2bfloat16(dv[u]);
+        dz[(int64_t)i * ld_dz] = h;
+        dzt[i] = h;
+      }
       local += dv[u];
     }
   }
@@ -505,9 +510,10 @@ int pbx_ctr_head_fwd(const float* tower, int ld_tower, const float* extra, const
 }
 
 int pbx_ctr_head_bwd(const float* dlogit, const float* gloss, int B, float* d_tower, float* d_extra, float* d_bias,
-                     int accumulate, cudaStream_t st) {
+                     int accumulate, void* dz_bf16, int ld_dz, void* dzt_bf16, cudaStream_t st) {
   if (B <= 0) return 0;
-  k_ctr_head_bwd<<<1, 1024, 0, st>>>(dlogit, gloss, B, d_tower, d_extra, d_bias, accumulate);
+  k_ctr_head_bwd<<<1, 1024, 0, st>>>(dlogit, gloss, B, d_tower, d_extra, d_bias, accumulate,
+                                     (__nv_bfloat16*)dz_bf16, ld_dz, (__nv_bfloat16*)dzt_bf16);
   PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }

@@ -36,9 +36,24 @@ __device__ __forceinline__ bool keep_key(const PbxSeqpoolParams& p, const float*
 }
 
 // one thread per (bag, concat block, source column)
+// optional tail: dense features copied into columns [off, off + cols) of the same output rows
+// (the tower input is [pooled slots | dense features] in one buffer: no separate copy launch)
+struct SeqpoolTail { const float* src; int ld, cols, off; };
+__device__ __forceinline__ void seqpool_copy_tail(const SeqpoolTail& t, int B, float* __restrict__ out,
+                                                  int out_stride) {
+  if (!t.src) return;
+  const int64_t total = (int64_t)B * t.cols;
+  for (int64_t it = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; it < total;
+       it += (int64_t)gridDim.x * blockDim.x) {
+    const int b = (int)(it / t.cols), c = (int)(it % t.cols);
+    out[(int64_t)b * out_stride + t.off + c] = __ldg(t.src + (int64_t)b * t.ld + c);
+  }
+}
+
 __global__ void k_seqpool_cvm_fwd(PbxSeqpoolParams p, const float* __restrict__ x,
                                   const uint32_t* __restrict__ restore, const int32_t* __restrict__ lod,
-                                  float* __restrict__ out) {
+                                  float* __restrict__ out, SeqpoolTail tail) {
+  seqpool_copy_tail(tail, p.B, out, p.out_stride);
   const int H = p.hidden;
   const int64_t per_bag = (int64_t)p.concat * H;
   const int64_t total = (int64_t)p.S * p.B * per_bag;
@@ -110,7 +125,8 @@ __global__ void k_seqpool_cvm_fwd(PbxSeqpoolParams p, const float* __restrict__ 
 // of the value rows, CVM transform applied in the chunk that holds show/clk.
 __global__ void k_seqpool_cvm_fwd_fast(PbxSeqpoolParams p, const float* __restrict__ x,
                                        const uint32_t* __restrict__ restore, const int32_t* __restrict__ lod,
-                                       float* __restrict__ out) {
+                                       float* __restrict__ out, SeqpoolTail tail) {
+  seqpool_copy_tail(tail, p.B, out, p.out_stride);
   const int H = p.hidden;
   const int chunks = (H + 3) >> 2;
   const int64_t total = (int64_t)p.S * p.B * chunks;
@@ -212,8 +228,21 @@ __global__ void k_key2slot(const int32_t* __restrict__ lod, int B, int S, int64_
 
 extern "C" {
 
+int pbx_seqpool_cvm_fwd_tail(const PbxSeqpoolParams* p, const float* d_x, const uint32_t* d_restore,
+                             const int32_t* d_lod, float* d_out, const float* d_tail, int tail_ld, int tail_cols,
+                             int tail_off, cudaStream_t st);
 int pbx_seqpool_cvm_fwd(const PbxSeqpoolParams* p, const float* d_x, const uint32_t* d_restore,
                         const int32_t* d_lod, float* d_out, cudaStream_t st) {
+  return pbx_seqpool_cvm_fwd_tail(p, d_x, d_restore, d_lod, d_out, nullptr, 0, 0, 0, st);
+}
+
+// The same, and d_tail [B, tail_cols] (row stride tail_ld) is copied into columns
+// [tail_off, tail_off + tail_cols) of every output row by the same launch.
+int pbx_seqpool_cvm_fwd_tail(const PbxSeqpoolParams* p, const float* d_x, const uint32_t* d_restore,
+                             const int32_t* d_lod, float* d_out, const float* d_tail, int tail_ld, int tail_cols,
+                             int tail_off, cudaStream_t st) {
+  SeqpoolTail tail{d_tail, tail_ld, tail_cols, tail_off};
+  if (d_tail) PBX_REQUIRE(tail_off + tail_cols <= p->out_stride, "seqpool tail exceeds the output row");
   PBX_REQUIRE(p->concat >= 1 && p->Eo % p->concat == 0, "bad embedx_concate_size");
   int64_t total = (int64_t)p->S * p->B * p->concat * p->hidden;
   if (total == 0) return 0;
@@ -224,11 +253,11 @@ int pbx_seqpool_cvm_fwd(const PbxSeqpoolParams* p, const float* d_x, const uint3
                     ((uintptr_t)d_x & 15) == 0;
   if (fast) {
     int64_t items = (int64_t)p->S * p->B * chunks;
-    k_seqpool_cvm_fwd_fast<<<pbx_grid_for(items, 256, 16), 256, 0, st>>>(*p, d_x, d_restore, d_lod, d_out);
+    k_seqpool_cvm_fwd_fast<<<pbx_grid_for(items, 256, 16), 256, 0, st>>>(*p, d_x, d_restore, d_lod, d_out, tail);
     PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
     return 0;
   }
-  k_seqpool_cvm_fwd<<<pbx_grid_for(total, 256, 16), 256, 0, st>>>(*p, d_x, d_restore, d_lod, d_out);
+  k_seqpool_cvm_fwd<<<pbx_grid_for(total, 256, 16), 256, 0, st>>>(*p, d_x, d_restore, d_lod, d_out, tail);
   PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }

@@ -89,6 +89,11 @@ int pbx_sparse_push_emu(void* const* ctxs, int nranks, const uint32_t* const* d_
  * _with_conv/_with_credit/_with_diff_thres/_tradew variants. */
 int pbx_seqpool_cvm_fwd(const PbxSeqpoolParams* p, const float* d_x, const uint32_t* d_restore,
                         const int32_t* d_lod, float* d_out, pbx_stream_t stream);
+/* the same launch also copies d_tail [B, tail_cols] (row stride tail_ld) into columns
+ * [tail_off, tail_off + tail_cols) of every output row (dense features next to the pooled slots) */
+int pbx_seqpool_cvm_fwd_tail(const PbxSeqpoolParams* p, const float* d_x, const uint32_t* d_restore,
+                             const int32_t* d_lod, float* d_out, const float* d_tail, int tail_ld, int tail_cols,
+                             int tail_off, pbx_stream_t stream);
 int pbx_seqpool_cvm_bwd(const PbxSeqpoolParams* p, const float* d_dout, const float* d_cvm,
                         const int32_t* d_lod, float* d_dx, int dx_stride, pbx_stream_t stream);
 int pbx_pull_scatter(const float* d_vals, int vstride, const uint32_t* d_restore, int64_t n, int hidden, int skip,
@@ -130,8 +135,10 @@ int pbx_sigmoid_logloss(const float* logit, const float* label, int B, float* pr
  * *gloss and writes (accumulate: adds) its sum to *d_bias.  extra / bias / d_* may be NULL. */
 int pbx_ctr_head_fwd(const float* tower, int ld_tower, const float* extra, const float* bias, const float* label,
                      int ld_label, int B, float* pred, float* loss_out, float* dlogit, pbx_stream_t stream);
+/* dz_bf16 [B, ld_dz] / dzt_bf16 [>= B] (optional): bf16 copies of the tower gradient written straight
+ * into the operands of the tower's last-layer backward GEMMs (saves a cast launch) */
 int pbx_ctr_head_bwd(const float* dlogit, const float* gloss, int B, float* d_tower, float* d_extra, float* d_bias,
-                     int accumulate, pbx_stream_t stream);
+                     int accumulate, void* dz_bf16, int ld_dz, void* dzt_bf16, pbx_stream_t stream);
 int pbx_fm_fwd(const float* x, int ldx, int B, int S, int E, int wcol, int vcol, int D, float* fm,
                pbx_stream_t stream);
 int pbx_fm_bwd(const float* x, int ldx, const float* g, int B, int S, int E, int wcol, int vcol, int D, float* dx,

@@ -90,7 +90,7 @@ class CtrDnn(CTRModelBase):
 
     def forward(self, batch: SlotBatch):
         x, _, labels = self.features(batch)
-        loss, pred = F.ctr_head(self.tower(x), labels[:, 0])
+        loss, pred = F.ctr_head(self.tower(x), labels[:, 0], tower_mod=self.tower)
         return loss, {"pred": pred, "label": labels[:, 0]}
 
 
@@ -109,7 +109,7 @@ class WideDeep(CTRModelBase):
         wide = pooled[:, 2::E].sum(1)                                   # sum of embed_w over slots
         if self.dense_dim:
             wide = wide + x[:, self.sparse_width:] @ self.wide_dense
-        loss, pred = F.ctr_head(self.tower(x), labels[:, 0], extra=wide, bias=self.wide_bias)
+        loss, pred = F.ctr_head(self.tower(x), labels[:, 0], extra=wide, bias=self.wide_bias, tower_mod=self.tower)
         return loss, {"pred": pred, "label": labels[:, 0]}
 
 
@@ -130,7 +130,7 @@ class DeepFM(CTRModelBase):
         else:
             fm = F.fm_interaction(pooled, self.num_slots, E, 2, 3, self.embedx_dim)
             deep = self.tower(x)
-        loss, pred = F.ctr_head(deep, labels[:, 0], extra=fm, bias=self.bias)
+        loss, pred = F.ctr_head(deep, labels[:, 0], extra=fm, bias=self.bias, tower_mod=self.tower)
         return loss, {"pred": pred, "label": labels[:, 0]}
 
 
@@ -158,7 +158,7 @@ class MMoE(CTRModelBase):
         for t in range(self.num_tasks):
             g = torch.softmax(gate_logits[:, t], dim=1)        # [B, E]
             mix = torch.einsum("be,ebh->bh", g, ex)
-            l, p = F.ctr_head(self.towers[t](mix), labels[:, t])
+            l, p = F.ctr_head(self.towers[t](mix), labels[:, t], tower_mod=self.towers[t])
             losses.append(l)
             preds.append(p)
         loss = torch.stack(losses).sum()

@@ -195,9 +195,10 @@ class _CtrHead(torch.autograd.Function):
     with their weights), so autograd launches no accumulation kernel for it."""
 
     @staticmethod
-    def forward(ctx, tower, extra, bias, label):
+    def forward(ctx, tower, extra, bias, label, tower_mod=None):
         B = tower.shape[0]
         assert tower.dim() in (1, 2) and (tower.dim() == 1 or tower.shape[1] == 1)
+        ctx.tower_mod = tower_mod
         dev = tower.device
         pred = torch.empty(B, dtype=torch.float32, device=dev)
         loss = torch.empty((), dtype=torch.float32, device=dev)
@@ -223,7 +224,7 @@ class _CtrHead(torch.autograd.Function):
         B = dlogit.numel()
         dev = dlogit.device
         if gloss is None:
-            return None, None, None, None
+            return None, None, None, None, None
         need_t = ctx.needs_input_grad[0]
         need_e = ctx.needs_input_grad[1] and ctx.has_extra
         d_tower = torch.empty(ctx.shape, dtype=torch.float32, device=dev) if need_t else None
@@ -236,13 +237,20 @@ class _CtrHead(torch.autograd.Function):
                 d_bias_ret = d_bias_ptr = torch.empty(1, dtype=torch.float32, device=dev)
         elif ctx.bias_nonleaf and ctx.needs_input_grad[2]:
             d_bias_ret = d_bias_ptr = torch.empty(1, dtype=torch.float32, device=dev)
+        # the tower that produced `tower` (a FusedMLP ending in one linear unit) takes its output
+        # gradient as bf16 operands: write them here instead of in a cast launch of its own
+        dz = dzt = None
+        slot = ctx.tower_mod.output_grad_slot(B) if (ctx.tower_mod is not None and need_t) else None
+        if slot is not None:
+            dz, dzt = slot
         N.check(N.cuda().pbx_ctr_head_bwd(N.ptr(dlogit), N.ptr(gloss.contiguous()), B, N.ptr(d_tower), N.ptr(d_extra),
-                                          N.ptr(d_bias_ptr), acc, N.stream_ptr()), "pbx_ctr_head_bwd")
-        return d_tower, d_extra, d_bias_ret, None
+                                          N.ptr(d_bias_ptr), acc, N.ptr(dz), dz.stride(0) if dz is not None else 0,
+                                          N.ptr(dzt), N.stream_ptr()), "pbx_ctr_head_bwd")
+        return d_tower, d_extra, d_bias_ret, None, None
 
 
 def ctr_head(tower: torch.Tensor, label: torch.Tensor, extra: torch.Tensor | None = None,
-             bias: torch.Tensor | None = None):
+             bias: torch.Tensor | None = None, tower_mod=None):
     """(mean log-loss, pred) of ``sigmoid(tower + extra + bias)`` against ``label``.
 
     ``tower`` [B] or [B, 1] (the last tower layer's output), ``extra`` [B] further logit terms
@@ -254,7 +262,7 @@ def ctr_head(tower: torch.Tensor, label: torch.Tensor, extra: torch.Tensor | Non
         if bias is not None:
             z = z + bias
         return sigmoid_log_loss(z, label)
-    return _CtrHead.apply(tower, extra, bias, label)
+    return _CtrHead.apply(tower, extra, bias, label, tower_mod)
 
 
 # ------------------------------------------------------------------ misc CTR utilities

@@ -261,13 +261,26 @@ class FusedMLP(nn.Module):
         self._last_out = out if self.final_relu else None
         return out
 
+    def output_grad_slot(self, B: int):
+        """(dZ [B, pad8(1)], dZt [1, pad8(B)]) of the last layer when a loss head may write the
+        output gradient straight into them as bf16 (single linear output unit); else None."""
+        ws = self._cur
+        if ws is None or ws.B != B or self.dims[-1] != 1 or self.final_relu:
+            return None
+        self._dz_ready = True
+        L = len(self.weights)
+        return ws.dZ[L - 1], ws.dZt[L - 1]
+
     def _backward_cuda(self, dout: torch.Tensor, need_dx: bool):
         ws = self._cur
         B = ws.B
         L = len(self.weights)
         if self.final_relu:
             dout = dout * (self._last_out > 0)
-        cast_transpose(dout, ws.dZ[L - 1], ws.dZt[L - 1])
+        if getattr(self, "_dz_ready", False):
+            self._dz_ready = False          # the loss head already wrote the bf16 operands
+        else:
+            cast_transpose(dout, ws.dZ[L - 1], ws.dZt[L - 1])
         dx = None
         wgrads = []
         for l in range(L - 1, -1, -1):

@@ -152,8 +152,11 @@ class _SparseEmbeddingPool(torch.autograd.Function):
         if dense is not None and vals.is_cuda:
             # pooled embeddings and dense features land in ONE row-major buffer: no concat pass
             out = torch.empty(B, sw + dense.shape[1], dtype=torch.float32, device=vals.device)
-            seqpool_cvm_forward(vals, batch.lod, B, S, attrs, box.hidden, restore=restore, out=out)
-            out[:, sw:] = dense
+            if dense.stride(1) == 1 and dense.dtype == torch.float32:
+                seqpool_cvm_forward(vals, batch.lod, B, S, attrs, box.hidden, restore=restore, out=out, tail=dense)
+            else:
+                seqpool_cvm_forward(vals, batch.lod, B, S, attrs, box.hidden, restore=restore, out=out)
+                out[:, sw:] = dense
         else:
             out = seqpool_cvm_forward(vals, batch.lod, B, S, attrs, box.hidden, restore=restore)
             if dense is not None:

@@ -87,8 +87,10 @@ def _params(a: SeqpoolAttrs, B, S, hidden, x_stride, out_stride) -> N.SeqpoolPar
 
 
 def seqpool_cvm_forward(x: torch.Tensor, lod: torch.Tensor, B: int, S: int, attrs: SeqpoolAttrs, hidden: int,
-                        restore: torch.Tensor | None = None, out: torch.Tensor | None = None) -> torch.Tensor:
-    """Raw forward.  ``x`` may be wider than ``hidden`` (row stride = x.shape[1])."""
+                        restore: torch.Tensor | None = None, out: torch.Tensor | None = None,
+                        tail: torch.Tensor | None = None) -> torch.Tensor:
+    """Raw forward.  ``x`` may be wider than ``hidden`` (row stride = x.shape[1]).  ``tail``
+    [B, Dd] (GPU, with ``out`` wide enough) is copied behind the pooled columns by the same launch."""
     Eo = attrs.out_width(hidden)
     if not x.is_cuda:
         rows = x[restore.long()] if restore is not None else x
@@ -96,6 +98,12 @@ def seqpool_cvm_forward(x: torch.Tensor, lod: torch.Tensor, B: int, S: int, attr
     if out is None:
         out = torch.empty(B, S * Eo, dtype=torch.float32, device=x.device)
     p = _params(attrs, B, S, hidden, x.stride(0), out.stride(0))
+    if tail is not None:
+        assert tail.stride(1) == 1 and tail.dtype == torch.float32 and out.shape[1] >= S * Eo + tail.shape[1]
+        N.check(N.cuda().pbx_seqpool_cvm_fwd_tail(C.byref(p), N.ptr(x), N.ptr(restore), N.ptr(lod), N.ptr(out),
+                                                  N.ptr(tail), tail.stride(0), tail.shape[1], S * Eo,
+                                                  N.stream_ptr()), "pbx_seqpool_cvm_fwd_tail")
+        return out
     N.check(N.cuda().pbx_seqpool_cvm_fwd(C.byref(p), N.ptr(x), N.ptr(restore), N.ptr(lod), N.ptr(out),
                                          N.stream_ptr()), "pbx_seqpool_cvm_fwd")
     return out

@@ -154,7 +154,11 @@ class CTRTrainer:
             self._after_batch(batch, loss, outs)
             return loss
         with t.span("backward+push"):
-            loss.backward()
+            # a cached root gradient: autograd does not launch a fill kernel for it every step
+            one = getattr(self, "_root_grad", None)
+            if one is None or one.device != loss.device or one.dtype != loss.dtype or one.shape != loss.shape:
+                one = self._root_grad = torch.ones_like(loss)
+            torch.autograd.backward(loss, grad_tensors=one)
         with t.span("dense_sync+opt"):
             self.sync.after_backward()
         self._after_batch(batch, loss, outs)
