@@ -456,7 +456,8 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
           if (locking && pending) {
             unsigned int* lk = reinterpret_cast<unsigned int*>(T.vals + (uint64_t)myrow * 32 + 31);
             got = atomicCAS(lk, 0u, 1u) == 0u;
-            if (got) __threadfence();            // acquire: row reads below must see the previous owner's stores
+            // (no acquire fence: the row is read with ld.cg from L2, the coherence point, in program
+            //  order after the CAS; the previous owner's stores reached L2 before its unlock)
           }
           const unsigned gmask = __ballot_sync(0xffffffffu, got);
           float4 rv[8];
@@ -532,7 +533,6 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
           if (locking && pending) {
             unsigned int* lk = reinterpret_cast<unsigned int*>(T.vals + (uint64_t)myrow * ST + ST - 1);
             got = atomicCAS(lk, 0u, 1u) == 0u;
-            if (got) __threadfence();
           }
           const unsigned gmask = __ballot_sync(0xffffffffu, got);
           for (int base = 0; base < nvec; base += 128) {   // 4 independent 16-byte loads per lane in flight
