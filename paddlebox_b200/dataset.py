@@ -343,7 +343,7 @@ class InMemoryDataset(DatasetBase):
     def set_max_rank(self, max_rank: int):
         self.max_rank = int(max_rank)
 
-    def host_batches(self, worker: int | None = None, prefetch: int = 3, with_ins_id: bool = False):
+    def host_batches(self, worker: int | None = None, prefetch: int = 4, with_ins_id: bool = False):
         """Iterate this worker's batches as pinned, record-major :class:`~paddlebox_b200.feed.HostBatch`
         es (no device work): the input of the pipelined feed ``CTRTrainer.train_host_batches``."""
         if self._prepared_workers == 0:

@@ -64,6 +64,7 @@ class PipelinedFeed:
     """Feeds :class:`HostBatch` es into a :class:`~paddlebox_b200.trainer.CTRTrainer`."""
 
     RING = 4
+    LAG = 2          # steps the host runs ahead of the loss read-back (< RING)
 
     def __init__(self, trainer, max_keys: int | None = None):
         self.trainer = trainer
@@ -160,24 +161,31 @@ class PipelinedFeed:
             on_loss(i, v)
 
     def run(self, host_batches: Iterable[HostBatch], on_loss: Callable[[int, float], None] | None = None,
-            collect: bool = True):
-        """Train on every host batch; returns (steps, instances, [loss per step])."""
+            collect: bool = True, after_enqueue: Callable[[int], None] | None = None):
+        """Train on every host batch; returns (steps, instances, [loss per step]).
+        ``after_enqueue(i)`` runs on the host right after step i was enqueued (stream-ordered work
+        put there executes between step i and step i+1)."""
         it = iter(host_batches)
         losses = [] if collect else None
         first = next(it, None)
         if first is None:
             return 0, 0, losses or []
-        i, n_ins, pending = 0, 0, None
+        i, n_ins, pending = 0, 0, []
         cur, cur_stage = first, self._enqueue_copy(0, first)
         while cur is not None:
             nxt = next(it, None)
             nxt_stage = self._enqueue_copy(i + 1, nxt) if nxt is not None else None   # overlaps step i
             done = self._enqueue_step(i, cur, cur_stage)
             n_ins += cur.batch_size
-            if pending is not None:
-                self._retire(pending, losses, on_loss)
-            pending = (i, cur, done)
+            if after_enqueue is not None:
+                after_enqueue(i)
+            pending.append((i, cur, done))
+            # the host stays LAG steps ahead of the loss it reads: enqueue jitter of one rank does
+            # not stall the (collective) step of all ranks
+            while len(pending) > self.LAG:
+                self._retire(pending.pop(0), losses, on_loss)
             cur, cur_stage = nxt, nxt_stage
             i += 1
-        self._retire(pending, losses, on_loss)
+        while pending:
+            self._retire(pending.pop(0), losses, on_loss)
         return i, n_ins, losses if losses is not None else []

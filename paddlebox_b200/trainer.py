@@ -212,7 +212,8 @@ class CTRTrainer:
             stats["stage_ms"] = self.timers.summary()   # read_time / cal_time style breakdown
         return stats
 
-    def train_host_batches(self, host_batches, on_loss=None, max_keys: int | None = None) -> dict:
+    def train_host_batches(self, host_batches, on_loss=None, max_keys: int | None = None,
+                           after_enqueue=None) -> dict:
         """Train on pinned host batches through the pipelined feed (``paddlebox_b200.feed``):
         H2D of batch i+1 overlaps step i, the batch is built straight into the buffers of the
         captured step graph (when ``enable_cuda_graph`` was called), and every step's loss is
@@ -222,7 +223,7 @@ class CTRTrainer:
         if feed is None:
             feed = self._feed = PipelinedFeed(self, max_keys)
         t0 = time.time()
-        steps, n_ins, losses = feed.run(host_batches, on_loss)
+        steps, n_ins, losses = feed.run(host_batches, on_loss, after_enqueue=after_enqueue)
         self.sync.finalize()
         dt = time.time() - t0
         return {"instances": n_ins, "seconds": dt, "ins_per_sec": n_ins / max(dt, 1e-9), "steps": steps,
