@@ -32,6 +32,35 @@ class PSGPUWrapper(BoxWrapper):
     def set_slot_dim_vector(self, dims) -> None:
         self.slot_dim_vector = list(dims)
 
+    # SetSparseSGD / SetEmbedxSGD (fleet/ps_gpu_wrapper.cu:139-187): the two halves of the sparse
+    # optimizer configuration, applied to the host tier and the HBM shard
+    def set_sparse_sgd(self, nonclk_coeff=0.1, clk_coeff=1.0, min_bound=-10.0, max_bound=10.0, learning_rate=0.05,
+                       initial_g2sum=3.0, initial_range=0.0, beta1_decay_rate=0.9, beta2_decay_rate=0.999,
+                       ada_epsilon=1e-8) -> None:
+        PSGPUWrapper._update_sparse_config(self, nonclk_coeff=nonclk_coeff, clk_coeff=clk_coeff, min_bound=min_bound,
+                                   max_bound=max_bound, learning_rate=learning_rate, initial_g2sum=initial_g2sum,
+                                   initial_range=initial_range, beta1_decay_rate=beta1_decay_rate,
+                                   beta2_decay_rate=beta2_decay_rate, ada_epsilon=ada_epsilon)
+
+    def set_embedx_sgd(self, mf_create_thresholds=10.0, mf_learning_rate=0.05, mf_initial_g2sum=3.0,
+                       mf_initial_range=1e-4, mf_min_bound=-10.0, mf_max_bound=10.0, mf_beta1_decay_rate=0.9,
+                       mf_beta2_decay_rate=0.999, mf_ada_epsilon=1e-8) -> None:
+        PSGPUWrapper._update_sparse_config(self, mf_create_thresholds=mf_create_thresholds, mf_learning_rate=mf_learning_rate,
+                                   mf_initial_g2sum=mf_initial_g2sum, mf_initial_range=mf_initial_range,
+                                   mf_min_bound=mf_min_bound, mf_max_bound=mf_max_bound,
+                                   mf_beta1_decay_rate=mf_beta1_decay_rate, mf_beta2_decay_rate=mf_beta2_decay_rate,
+                                   mf_ada_epsilon=mf_ada_epsilon)
+
+    def _update_sparse_config(self, **kw) -> None:
+        from . import _native as N
+        cur = self.host_table.config.as_dict() if getattr(self, "host_table", None) is not None else {}
+        cur.update(kw)
+        cfg = N.SparseOptConfig(**cur)
+        if getattr(self, "host_table", None) is not None:
+            self.host_table.set_config(cfg)
+        if getattr(self, "table", None) is not None:
+            self.table.set_config(cfg)
+
     def init_gpu_server(self, conf: dict | None = None, **kw) -> None:
         """``InitializeGPUServer``: sparse-SGD config from the fleet desc (ps_gpu_trainer.cc:137-254)."""
         self.initialize_gpu_and_load_model(conf or {}, **kw)

@@ -153,3 +153,23 @@ def test_merge_multi_models(tmp_path, box):
     box.merge_multi_models([str(tmp_path / "m1"), str(tmp_path / "m2")], update_type=1)
     r = box.host_table.fetch_rows(keys, create=False)
     assert np.allclose(r[:10, 0], 14.0) and np.allclose(r[:10, 1], 3.0) and np.allclose(r[:10, 2], -0.25)
+
+
+def test_psgpu_sparse_sgd_setters_reach_the_table(box):
+    from paddlebox_b200 import ps_gpu
+    w = ps_gpu.PSGPUWrapper.get_instance()
+    assert isinstance(w, BoxWrapper)
+    # the instance was created through BoxWrapper; the setters are plain functions over it
+    ps_gpu.PSGPUWrapper.set_sparse_sgd(w, learning_rate=0.2, initial_g2sum=1.0)
+    ps_gpu.PSGPUWrapper.set_embedx_sgd(w, mf_create_thresholds=2.0, mf_learning_rate=0.3)
+    cfg = w.host_table.config.as_dict()
+    assert abs(cfg["learning_rate"] - 0.2) < 1e-7 and abs(cfg["mf_learning_rate"] - 0.3) < 1e-7
+    assert abs(cfg["mf_create_thresholds"] - 2.0) < 1e-7 and abs(cfg["clk_coeff"] - 1.0) < 1e-7
+    # a push now uses the new learning rate: embed_w moves by lr * g / show * sqrt(g0/(g0+g2sum))
+    keys = np.array([77], dtype=np.uint64)
+    before = w.host_table.fetch_rows(keys, create=True).copy()
+    push = torch.zeros(1, w.host_table.layout.push_stride)
+    push[0, 1], push[0, 3] = 1.0, 1.0           # show 1, embed_g 1
+    w.host_table.push(keys, push)
+    after = w.host_table.fetch_rows(keys, create=False)
+    assert abs((after[0, 2] - before[0, 2]) - 0.2) < 1e-5
