@@ -82,6 +82,16 @@ def cast_transpose(x: torch.Tensor, out: torch.Tensor | None, out_t: torch.Tenso
 
 
 CT_MAX = 12
+_SIDE_STREAMS: dict = {}
+
+
+def _side_stream(device) -> "torch.cuda.Stream":
+    """One auxiliary stream per device for work that is off the critical path (weight gradients)."""
+    key = torch.device(device).index if torch.device(device).index is not None else torch.cuda.current_device()
+    st = _SIDE_STREAMS.get(key)
+    if st is None:
+        st = _SIDE_STREAMS[key] = torch.cuda.Stream(device=key)
+    return st
 
 
 def cast_transpose_multi(items) -> None:
@@ -283,6 +293,10 @@ class FusedMLP(nn.Module):
             cast_transpose(dout, ws.dZ[L - 1], ws.dZt[L - 1])
         dx = None
         wgrads = []
+        from ..flags import FLAGS
+        overlap = bool(FLAGS.pbx_overlap_wgrad) and gemm_impl() == 0
+        main = torch.cuda.current_stream(dout.device)
+        side = _side_stream(dout.device) if overlap else None
         for l in range(L - 1, -1, -1):
             K, Nn = self.dims[l], self.dims[l + 1]
             w, b = self.weights[l], self.biases[l]
@@ -291,18 +305,27 @@ class FusedMLP(nn.Module):
             if b.grad is None:
                 b.grad = torch.zeros_like(b.data)
             # wgrad: dW[N, K] += dZ^T[N, B] . (H^T[K, B])^T   (split-K over the batch)
-            splitk = max(1, min(16, B // 1024))     # two CTAs per SM in the grouped launch: one wave
             # (the ones row of Ht makes output column K the bias gradient: no separate column-sum pass)
-            # Weight gradients are off the critical path of the dgrad chain: they are collected
-            # and issued as ONE grouped launch once every dZ exists.
-            if ((Nn + 127) // 128) * ((K + 128) // 128) >= 148:
+            big = ((Nn + 127) // 128) * ((K + 128) // 128) >= 148
+            if overlap:
+                # Weight gradients are off the critical path: layer l's runs on the side stream as
+                # soon as dZ[l] exists, concurrently with the dgrad chain on the main stream (the
+                # tower GEMMs are latency-bound and leave most of the machine idle).
+                ev = torch.cuda.Event()
+                ev.record(main)
+                side.wait_event(ev)
+                with torch.cuda.stream(side):
+                    gemm_bf16_tn(ws.dZt[l], ws.Ht[l], Nn, K + 1, B, out_f32=w.grad, accumulate=True,
+                                 splitk=1 if big else max(1, min(16, B // 512)), col_out=b.grad, col_split=K)
+            elif big:
                 # already a full wave of output tiles: no split-K (no contended atomics), own
                 # launch with the wide 128x256 tile
                 gemm_bf16_tn(ws.dZt[l], ws.Ht[l], Nn, K + 1, B, out_f32=w.grad, accumulate=True, splitk=1,
                              col_out=b.grad, col_split=K)
             else:
+                # one grouped launch once every dZ exists (two CTAs per SM: one wave)
                 wgrads.append(gemm_problem(ws.dZt[l], ws.Ht[l], Nn, K + 1, B, out_f32=w.grad, accumulate=True,
-                                           splitk=splitk, col_out=b.grad, col_split=K))
+                                           splitk=max(1, min(16, B // 1024)), col_out=b.grad, col_split=K))
             if l > 0:
                 # dgrad fused with the ReLU mask of the previous activation
                 gemm_bf16_tn(ws.dZ[l], self._wbt[l], B, K, Nn, mask=ws.H[l], out_bf16=ws.dZ[l - 1],
@@ -312,7 +335,12 @@ class FusedMLP(nn.Module):
                 # odd stride it falls back to 4-byte stores that touch 32 rows per instruction)
                 dx = torch.empty(B, (K + 3) // 4 * 4, dtype=torch.float32, device=dout.device)[:, :K]
                 gemm_bf16_tn(ws.dZ[0], self._wbt[0], B, K, Nn, out_f32=dx)
-        if not wgrads:
+        if overlap:
+            done = torch.cuda.Event()
+            done.record(side)
+            self._wgrad_done = done         # joined by the caller after its own tail work
+            main.wait_event(done)
+        elif not wgrads:
             pass
         elif gemm_impl() == 0:
             gemm_bf16_tn_grouped(wgrads, block_n=64)
