@@ -47,6 +47,7 @@ def parse_args():
     p.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
     p.add_argument("--profile-stages", action="store_true")
     p.add_argument("--no-graph", action="store_true", help="do not capture the step in a CUDA graph")
+    p.add_argument("--timeline", default="", help="diagnosis only: write a CUPTI kernel timeline of 3 steps to this file")
     p.add_argument("--model", default="deepfm", choices=["deepfm", "wide_deep", "ctr_dnn", "mmoe"],
                    help="deepfm = BASELINE config 3 (the headline); wide_deep = config 2 (dim 8, 12.5M keys/GPU "
                         "= 100M over 8); mmoe = config 4 (300 slots, dim 64)")
@@ -286,6 +287,22 @@ def main():
     sparse_phases = box.engine.phase_times()      # last timed step, this rank
     loss_val = float(loss)
 
+    if args.timeline and rank == 0:
+        # diagnosis only (never a timing of record): kernel start/duration inside the replayed graph
+        from torch.profiler import ProfilerActivity, profile
+        with profile(activities=[ProfilerActivity.CUDA]) as prof:
+            for i in range(3):
+                flush()
+                trainer.train_step(dev_batches[i % len(dev_batches)])
+            torch.cuda.synchronize()
+        evs = sorted([(e.time_range.start, e.time_range.end - e.time_range.start, e.name) for e in prof.events()
+                      if e.device_type == torch.autograd.DeviceType.CUDA], key=lambda x: x[0])
+        with open(args.timeline, "w") as f:
+            prev_end = None
+            for st, du, nm in evs:
+                gap = (st - prev_end) if prev_end is not None else 0
+                f.write(f"{st}\t{du}\t{gap}\t{nm[:80]}\n")
+                prev_end = st + du
     # ------------------------------------------------ end-to-end through the public API
     # (CTRTrainer.train_host_batches): every step copies its inputs from pinned host memory
     # (copy stream, overlapping the previous step), builds the batch on the device, trains, and

@@ -117,16 +117,29 @@ __global__ void k_adam_flat(float* __restrict__ p, float* __restrict__ g, float*
   const float t = step_dev[0] + 1.f;
   const float c1 = 1.f - powf(b1, t), c2 = 1.f - powf(b2, t);
   const float step_size = lr * sqrtf(c2) / c1;
-  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    float gi = g[i] * grad_scale;
-    float pi = p[i];
+  auto upd = [&](float& pi, float& gi_, float& mi_, float& vi_) {
+    float gi = gi_ * grad_scale;
     if (weight_decay != 0.f) gi += weight_decay * pi;
-    float mi = b1 * m[i] + (1.f - b1) * gi;
-    float vi = b2 * v[i] + (1.f - b2) * gi * gi;
-    m[i] = mi;
-    v[i] = vi;
-    p[i] = pi - step_size * mi / (sqrtf(vi) + eps * sqrtf(c2));
-    if (zero_grad) g[i] = 0.f;
+    mi_ = b1 * mi_ + (1.f - b1) * gi;
+    vi_ = b2 * vi_ + (1.f - b2) * gi * gi;
+    pi = pi - step_size * mi_ / (sqrtf(vi_) + eps * sqrtf(c2));
+    if (zero_grad) gi_ = 0.f;
+  };
+  const int64_t tid = blockIdx.x * (int64_t)blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
+  const bool vec = ((((uintptr_t)p | (uintptr_t)g | (uintptr_t)m | (uintptr_t)v) & 15) == 0);
+  const int64_t n4 = vec ? n / 4 : 0;
+  for (int64_t i = tid; i < n4; i += nth) {        // 16-byte accesses: the flat buffers are 16-byte aligned
+    float4 P = reinterpret_cast<float4*>(p)[i], G = reinterpret_cast<float4*>(g)[i];
+    float4 M = reinterpret_cast<float4*>(m)[i], V = reinterpret_cast<float4*>(v)[i];
+    upd(P.x, G.x, M.x, V.x); upd(P.y, G.y, M.y, V.y); upd(P.z, G.z, M.z, V.z); upd(P.w, G.w, M.w, V.w);
+    reinterpret_cast<float4*>(p)[i] = P; reinterpret_cast<float4*>(m)[i] = M; reinterpret_cast<float4*>(v)[i] = V;
+    if (zero_grad) reinterpret_cast<float4*>(g)[i] = G;
+  }
+  for (int64_t i = n4 * 4 + tid; i < n; i += nth) {
+    float pi = p[i], gi = g[i], mi = m[i], vi = v[i];
+    upd(pi, gi, mi, vi);
+    p[i] = pi; m[i] = mi; v[i] = vi;
+    if (zero_grad) g[i] = gi;
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -266,6 +279,7 @@ k_fm_fwd(const float* __restrict__ x, int ldx, int B, int S, int E, int wcol, in
   const int warps = gridDim.x * nw;
   for (int b = blockIdx.x * nw + wib; b < B; b += warps) {
     const float* row = x + (int64_t)b * ldx;
+#pragma unroll 4
     for (int e = lane; e < W; e += 32) srow[e] = __ldg(row + e);
     __syncwarp();
     float acc = 0.f;
@@ -299,6 +313,7 @@ k_fm_bwd(const float* __restrict__ x, int ldx, const float* __restrict__ g, int 
   for (int b = blockIdx.x * nw + wib; b < B; b += warps) {
     const float* row = x + (int64_t)b * ldx;
     float* drow = dx + (int64_t)b * lddx;
+#pragma unroll 4
     for (int e = lane; e < W; e += 32) srow[e] = __ldg(row + e);
     const float gb = __ldg(g + b);
     __syncwarp();
@@ -308,13 +323,25 @@ k_fm_bwd(const float* __restrict__ x, int ldx, const float* __restrict__ g, int 
       ssum[d] = sv;
     }
     __syncwarp();
-    for (int e = lane; e < W; e += 32) {
-      const int c = e % E;
-      float gv;
-      if (c == wcol) gv = gb;
-      else if (c >= vcol && c < vcol + D) gv = gb * (ssum[c - vcol] - srow[e]);
-      else { if (accumulate) continue; gv = 0.f; }
-      drow[e] = accumulate ? drow[e] + gv : gv;
+    for (int e0 = lane; e0 < W; e0 += 128) {          // four independent read-modify-writes in flight
+      float gv[4], old[4];
+      bool on[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int e = e0 + 32 * u;
+        on[u] = e < W;
+        gv[u] = 0.f;
+        if (on[u]) {
+          const int c = e % E;
+          if (c == wcol) gv[u] = gb;
+          else if (c >= vcol && c < vcol + D) gv[u] = gb * (ssum[c - vcol] - srow[e]);
+          else if (accumulate) on[u] = false;
+        }
+        old[u] = (on[u] && accumulate) ? drow[e] : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (on[u]) drow[e0 + 32 * u] = old[u] + gv[u];
     }
     __syncwarp();
   }
@@ -530,8 +557,9 @@ int pbx_colsum_bf16(const void* x, int ld, int M, int N, float* out, cudaStream_
 int pbx_adam_flat(float* p, float* g, float* m, float* v, int64_t n, float lr, float b1, float b2, float eps,
                   float weight_decay, float grad_scale, float* step_dev, int zero_grad, cudaStream_t st) {
   if (n <= 0) return 0;
-  k_adam_flat<<<pbx_grid_for(n, 256, 8), 256, 0, st>>>(p, g, m, v, n, lr, b1, b2, eps, weight_decay, grad_scale,
-                                                       step_dev, zero_grad);
+  // (at most two blocks per SM: every block ends with one atomic on the step word)
+  k_adam_flat<<<pbx_grid_for((n + 3) / 4, 256, 2), 256, 0, st>>>(p, g, m, v, n, lr, b1, b2, eps, weight_decay, grad_scale,
+                                                                 step_dev, zero_grad);
   PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }
