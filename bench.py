@@ -47,6 +47,7 @@ def parse_args():
     p.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
     p.add_argument("--profile-stages", action="store_true")
     p.add_argument("--no-graph", action="store_true", help="do not capture the step in a CUDA graph")
+    p.add_argument("--e2e-debug", action="store_true", help="diagnosis only: time the end-to-end loop with parts disabled")
     p.add_argument("--timeline", default="", help="diagnosis only: write a CUPTI kernel timeline of 3 steps to this file")
     p.add_argument("--model", default="deepfm", choices=["deepfm", "wide_deep", "ctr_dnn", "mmoe"],
                    help="deepfm = BASELINE config 3 (the headline); wide_deep = config 2 (dim 8, 12.5M keys/GPU "
@@ -342,14 +343,36 @@ def main():
     ea2, eb2 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     ea2.record()
+    hq0, hw0 = feed.host_enqueue_s, feed.host_wait_s
     trainer.train_host_batches(host_iter(5, args.steps), on_loss=None, max_keys=max_keys)
     eb2.record()
+    host_us = ((feed.host_enqueue_s - hq0) / args.steps * 1e6, (feed.host_wait_s - hw0) / args.steps * 1e6)
     barrier()
     e2e_nf_ms = ea2.elapsed_time(eb2)
     h2d_bytes = (feed.h2d_bytes - h0) // args.steps
     d2h_bytes = (feed.d2h_bytes - d0) // args.steps
     clocks = sampler.stop()
     box.engine.check_status()
+
+    if args.e2e_debug:
+        for tag, kw in [("full", {}), ("no_h2d", {"debug_skip_h2d": True}), ("no_d2h", {"debug_skip_d2h": True}),
+                        ("no_build", {"debug_skip_h2d": True, "debug_skip_build": True}),
+                        ("none", {"debug_skip_h2d": True, "debug_skip_build": True, "debug_skip_d2h": True})]:
+            for k in ("debug_skip_h2d", "debug_skip_d2h", "debug_skip_build"):
+                setattr(feed, k, kw.get(k, False))
+            x0, x1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            x0.record()
+            trainer.train_host_batches(host_iter(7, args.steps), on_loss=None, max_keys=max_keys)
+            x1.record()
+            barrier()
+            tt = torch.tensor([x0.elapsed_time(x1)], dtype=torch.float64, device=dev)
+            if world > 1:
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+            if rank == 0:
+                print(f"e2e-debug {tag}: {float(tt) / args.steps * 1e3:.1f} us/step", file=sys.stderr, flush=True)
+        for k in ("debug_skip_h2d", "debug_skip_d2h", "debug_skip_build"):
+            setattr(feed, k, False)
 
     # max over ranks
     t = torch.tensor([dev_ms, e2e_ms, e2e_nf_ms], dtype=torch.float64, device=dev)
@@ -381,7 +404,9 @@ def main():
             "e2e": {"value": round(e2e, 1), "unit": "instances/s", "ms_per_step": round(e2e_ms / args.steps, 4),
                     "h2d_bytes_per_step": int(h2d_bytes), "d2h_bytes_per_step": int(d2h_bytes),
                     "no_l2_flush": {"value": round(gb * args.steps / (e2e_nf_ms / 1e3), 1),
-                                    "ms_per_step": round(e2e_nf_ms / args.steps, 4)},
+                                    "ms_per_step": round(e2e_nf_ms / args.steps, 4),
+                                    "host_enqueue_us_per_step_rank0": round(host_us[0], 1),
+                                    "host_wait_us_per_step_rank0": round(host_us[1], 1)},
                     "timed_region": "one CUDA-event pair around all K pipelined steps incl. H2D of every "
                                     "batch, batch_build, step, per-step loss D2H and the per-step L2 flush"},
             "gpu_launches": int(launches),

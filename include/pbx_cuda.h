@@ -158,6 +158,8 @@ int pbx_auc_bucket(const float* pred, const float* label, const float* mask, int
                    double* table, double* sums, pbx_stream_t stream);
 /* reference: fleet/box_wrapper.cu:1210-1224 */
 int pbx_row_gather(const float* table, const int64_t* idx, int64_t n, int dim, float* out, pbx_stream_t stream);
+/* n floats device -> pinned host memory by a device-side store (no copy-engine hop) */
+int pbx_store_host(const float* d_src, float* pinned_dst, int n, pbx_stream_t stream);
 int pbx_l2_flush(void* buf, int64_t bytes, pbx_stream_t stream);
 
 /* ---- device-side batch construction (csrc/cuda/batch_build.cu) ----------------

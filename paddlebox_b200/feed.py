@@ -19,6 +19,7 @@ hidden but every step's loss still reaches the host.
 from __future__ import annotations
 
 import ctypes as C
+import time
 from dataclasses import dataclass
 from typing import Callable, Iterable, Optional
 
@@ -77,6 +78,11 @@ class PipelinedFeed:
         self._tgt: SlotBatch | None = None
         self.h2d_bytes = 0
         self.d2h_bytes = 0
+        self.debug_skip_h2d = False   # diagnosis switches (benchmarks only)
+        self.debug_skip_d2h = False
+        self.debug_skip_build = False
+        self.host_enqueue_s = 0.0     # host time spent enqueueing work
+        self.host_wait_s = 0.0        # host time spent waiting for the device (0 => the host is the bottleneck)
 
     # -- buffers ---------------------------------------------------------------------------
     def _target(self, hb: HostBatch) -> SlotBatch:
@@ -110,6 +116,8 @@ class PipelinedFeed:
         if hb.n_keys > self.max_keys:
             raise ValueError(f"batch has {hb.n_keys} keys; the feed was sized for {self.max_keys}")
         s = self._stage(i, hb)
+        if self.debug_skip_h2d and i >= 2:          # diagnosis only: reuse what the stage already holds
+            return s
         cp = self.copy_stream
         cp.wait_event(s.built)                      # the stage's previous reader is done
         with torch.cuda.stream(cp):
@@ -127,10 +135,11 @@ class PipelinedFeed:
         main.wait_event(s.copied)
         tgt = self._target(hb)
         B, S = hb.batch_size, hb.num_slots
-        N.check(N.cuda().pbx_batch_build(N.ptr(s.keys), N.ptr(s.offsets), B, S, N.ptr(tgt.keys), N.ptr(tgt.lod),
-                                         N.ptr(self.scratch), N.stream_ptr(main)), "pbx_batch_build")
-        if hb.dense is not None:
-            tgt.dense.copy_(s.dense, non_blocking=True)
+        if not (self.debug_skip_build and i >= 2):
+            N.check(N.cuda().pbx_batch_build(N.ptr(s.keys), N.ptr(s.offsets), B, S, N.ptr(tgt.keys), N.ptr(tgt.lod),
+                                             N.ptr(self.scratch), N.stream_ptr(main)), "pbx_batch_build")
+            if hb.dense is not None:
+                tgt.dense.copy_(s.dense, non_blocking=True)
         s.built.record(main)
         tgt.ins_ids = hb.ins_ids
         tgt.meta = hb.meta
@@ -143,15 +152,21 @@ class PipelinedFeed:
                               ins_ids=hb.ins_ids, meta=hb.meta)
             loss = tr._eager_step(batch)
         slot = i % self.RING
-        self.loss_pin[slot:slot + 1].copy_(loss.detach().reshape(1), non_blocking=True)
-        self.d2h_bytes += 4
+        if not self.debug_skip_d2h:
+            # the device stores the loss into the pinned ring itself (a copy-engine D2H between two
+            # graph launches costs ~10 us of stream latency)
+            N.check(N.cuda().pbx_store_host(N.ptr(loss.detach()), C.c_void_p(self.loss_pin.data_ptr() + 4 * slot), 1,
+                                            N.stream_ptr(main)), "pbx_store_host")
+            self.d2h_bytes += 4
         done = torch.cuda.Event()
         done.record(main)
         return done
 
     def _retire(self, pending, losses, on_loss):
         i, hb, done = pending
+        t0 = time.perf_counter()
         done.synchronize()
+        self.host_wait_s += time.perf_counter() - t0
         v = float(self.loss_pin[i % self.RING])
         if hb.release is not None:
             hb.release()
@@ -173,9 +188,11 @@ class PipelinedFeed:
         i, n_ins, pending = 0, 0, []
         cur, cur_stage = first, self._enqueue_copy(0, first)
         while cur is not None:
+            t0 = time.perf_counter()
             nxt = next(it, None)
             nxt_stage = self._enqueue_copy(i + 1, nxt) if nxt is not None else None   # overlaps step i
             done = self._enqueue_step(i, cur, cur_stage)
+            self.host_enqueue_s += time.perf_counter() - t0
             n_ins += cur.batch_size
             if after_enqueue is not None:
                 after_enqueue(i)

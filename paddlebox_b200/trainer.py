@@ -227,7 +227,8 @@ class CTRTrainer:
         self.sync.finalize()
         dt = time.time() - t0
         return {"instances": n_ins, "seconds": dt, "ins_per_sec": n_ins / max(dt, 1e-9), "steps": steps,
-                "losses": losses, "h2d_bytes": feed.h2d_bytes, "d2h_bytes": feed.d2h_bytes}
+                "losses": losses, "h2d_bytes": feed.h2d_bytes, "d2h_bytes": feed.d2h_bytes,
+                "host_enqueue_s": feed.host_enqueue_s, "host_wait_s": feed.host_wait_s}
 
     def finalize(self):
         if self.dumper is not None:
