@@ -281,8 +281,8 @@ def main():
     barrier()
     wall = time.time() - wall0
     launches = lib.pbx_launch_count() - launches0 - (0 if args.no_flush else args.steps)
-    if graphed:   # launches replayed from the graph are not seen by the host-side counter
-        launches = launches_per_step * args.steps
+    if graphed:   # launches replayed from the graph are not seen by the host-side counter (the copy
+        launches = launches_per_step * args.steps + launches       # into the static buffers is)
     dev_ms = sum(a.elapsed_time(b) for a, b in evs)
     box.engine.check_status()
     sparse_phases = box.engine.phase_times()      # last timed step, this rank

@@ -477,6 +477,19 @@ __global__ void k_store_host(const float* __restrict__ src, float* __restrict__ 
   __threadfence_system();
 }
 
+// keys + lod + dense of one mini-batch into the static buffers of the captured step: ONE launch
+// instead of three device-to-device copies
+__global__ void k_copy_batch(const int4* __restrict__ k_src, int4* __restrict__ k_dst, int64_t k16,
+                             const int* __restrict__ l_src, int* __restrict__ l_dst, int64_t nl,
+                             const float* __restrict__ d_src, float* __restrict__ d_dst, int64_t nd) {
+  const int64_t tid = blockIdx.x * (int64_t)blockDim.x + threadIdx.x, nth = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = tid; i < (k16 >> 1); i += nth) k_dst[i] = k_src[i];      // k16 = number of 64-bit ids here
+  if ((k16 & 1) && tid == 0)
+    reinterpret_cast<long long*>(k_dst)[k16 - 1] = reinterpret_cast<const long long*>(k_src)[k16 - 1];
+  for (int64_t i = tid; i < nl; i += nth) l_dst[i] = l_src[i];
+  for (int64_t i = tid; i < nd; i += nth) d_dst[i] = d_src[i];
+}
+
 // L2 flush helper for benches: writes a buffer larger than L2
 __global__ void k_fill_u32(uint32_t* p, int64_t n, uint32_t v) {
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
@@ -664,6 +677,21 @@ int pbx_row_gather(const float* table, const int64_t* idx, int64_t n, int dim, f
 int pbx_store_host(const float* d_src, float* pinned_dst, int n, cudaStream_t st) {
   if (n <= 0) return 0;
   k_store_host<<<1, 32, 0, st>>>(d_src, pinned_dst, n);
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
+  return 0;
+}
+
+// keys: n_keys 64-bit ids (both buffers 16-byte aligned); lod: n_lod int32;
+// dense: n_dense floats (src/dst may be NULL with n_dense = 0)
+int pbx_copy_batch(const void* keys_src, void* keys_dst, int64_t n_keys, const int32_t* lod_src, int32_t* lod_dst,
+                   int64_t n_lod, const float* dense_src, float* dense_dst, int64_t n_dense, cudaStream_t st) {
+  PBX_REQUIRE((((uintptr_t)keys_src | (uintptr_t)keys_dst) & 15) == 0, "copy_batch: key buffers must be 16-byte aligned");
+  const int64_t k16 = n_keys;
+  int64_t work = n_keys / 2 + 1 > n_lod ? n_keys / 2 + 1 : n_lod;
+  if (n_dense > work) work = n_dense;
+  if (work <= 0) return 0;
+  k_copy_batch<<<pbx_grid_for(work, 256, 4), 256, 0, st>>>((const int4*)keys_src, (int4*)keys_dst, k16, lod_src, lod_dst,
+                                                            n_lod, dense_src, dense_dst, n_dense);
   PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }

@@ -158,6 +158,10 @@ int pbx_auc_bucket(const float* pred, const float* label, const float* mask, int
                    double* table, double* sums, pbx_stream_t stream);
 /* reference: fleet/box_wrapper.cu:1210-1224 */
 int pbx_row_gather(const float* table, const int64_t* idx, int64_t n, int dim, float* out, pbx_stream_t stream);
+/* one launch copies a mini-batch (keys, lod, dense) into the static buffers of a captured step;
+ * key buffers 16-byte aligned */
+int pbx_copy_batch(const void* keys_src, void* keys_dst, int64_t n_keys, const int32_t* lod_src, int32_t* lod_dst,
+                   int64_t n_lod, const float* dense_src, float* dense_dst, int64_t n_dense, pbx_stream_t stream);
 /* n floats device -> pinned host memory by a device-side store (no copy-engine hop) */
 int pbx_store_host(const float* d_src, float* pinned_dst, int n, pbx_stream_t stream);
 int pbx_l2_flush(void* buf, int64_t bytes, pbx_stream_t stream);
