@@ -50,8 +50,12 @@ __device__ __forceinline__ int block_exscan(int v, int* total) {
 
 __global__ void __launch_bounds__(BB_THREADS)
 k_batch_build(const uint64_t* __restrict__ rec_keys, const int32_t* __restrict__ rec_off, int B, int S,
-              uint64_t* __restrict__ keys_out, int32_t* __restrict__ lod_out, int32_t* __restrict__ block_sums) {
+              uint64_t* __restrict__ keys_out, int32_t* __restrict__ lod_out, int32_t* __restrict__ block_sums,
+              const float* __restrict__ dense_src, float* __restrict__ dense_dst, int64_t n_dense) {
   cg::grid_group grid = cg::this_grid();
+  // optional: the batch's dense block (labels + dense features) moves with the same launch
+  for (int64_t i = blockIdx.x * (int64_t)BB_THREADS + threadIdx.x; i < n_dense; i += (int64_t)gridDim.x * BB_THREADS)
+    dense_dst[i] = dense_src[i];
   const int G = S * B;
   const int per_block = (G + gridDim.x - 1) / gridDim.x;
   const int g0 = blockIdx.x * per_block, g1 = min(G, g0 + per_block);
@@ -122,16 +126,27 @@ extern "C" {
 
 // d_rec_off: [B, S+1] global offsets into d_rec_keys (record-major CSR).
 // d_scratch: >= 1024 int32 of scratch for the cross-block scan.
+int pbx_batch_build_dense(const uint64_t* d_rec_keys, const int32_t* d_rec_off, int B, int S, uint64_t* d_keys_out,
+                          int32_t* d_lod_out, int32_t* d_scratch, const float* d_dense_src, float* d_dense_dst,
+                          int64_t n_dense, cudaStream_t st);
 int pbx_batch_build(const uint64_t* d_rec_keys, const int32_t* d_rec_off, int B, int S, uint64_t* d_keys_out,
                     int32_t* d_lod_out, int32_t* d_scratch, cudaStream_t st) {
+  return pbx_batch_build_dense(d_rec_keys, d_rec_off, B, S, d_keys_out, d_lod_out, d_scratch, nullptr, nullptr, 0, st);
+}
+
+// The same launch also copies n_dense floats d_dense_src -> d_dense_dst (the batch's label + dense block).
+int pbx_batch_build_dense(const uint64_t* d_rec_keys, const int32_t* d_rec_off, int B, int S, uint64_t* d_keys_out,
+                          int32_t* d_lod_out, int32_t* d_scratch, const float* d_dense_src, float* d_dense_dst,
+                          int64_t n_dense, cudaStream_t st) {
   if (B <= 0 || S <= 0) return 0;
   int G = S * B;
   int blocks = (G + BB_THREADS - 1) / BB_THREADS;   // one bag per thread while the SMs last
   int sms = pbx_num_sms();
   if (blocks > sms) blocks = sms;
   if (blocks < 1) blocks = 1;
+  if (!d_dense_src || !d_dense_dst) n_dense = 0;
   void* args[] = {(void*)&d_rec_keys, (void*)&d_rec_off, (void*)&B, (void*)&S, (void*)&d_keys_out,
-                  (void*)&d_lod_out, (void*)&d_scratch};
+                  (void*)&d_lod_out, (void*)&d_scratch, (void*)&d_dense_src, (void*)&d_dense_dst, (void*)&n_dense};
   PBX_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_batch_build, dim3(blocks), dim3(BB_THREADS), args, 0, st));
   pbx_note_launch(1);
   return 0;
@@ -218,8 +233,11 @@ int pbx_batch_build_static(const uint64_t* d_rec_keys, const int32_t* d_rec_off,
   int sms = pbx_num_sms();
   if (blocks > sms) blocks = sms;
   if (blocks < 1) blocks = 1;   // blocks <= 512 = PBX_BB_STATIC_SCRATCH_INTS by the check above
+  const float* no_src = nullptr;
+  float* no_dst = nullptr;
+  int64_t no_n = 0;
   void* args[] = {(void*)&d_rec_keys, (void*)&d_rec_off, (void*)&B, (void*)&S, (void*)&d_keys_out,
-                  (void*)&d_lod_out, (void*)&scratch};
+                  (void*)&d_lod_out, (void*)&scratch, (void*)&no_src, (void*)&no_dst, (void*)&no_n};
   PBX_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_batch_build, dim3(blocks), dim3(BB_THREADS), args, 0, st));
   pbx_note_launch(1);
   return 0;

@@ -170,6 +170,10 @@ int pbx_l2_flush(void* buf, int64_t bytes, pbx_stream_t stream);
  * reference: data_feed.cu:1208-1384, data_feed.cc:3400-3522, :4896-4940 */
 int pbx_batch_build(const uint64_t* d_rec_keys, const int32_t* d_rec_off, int B, int S, uint64_t* d_keys_out,
                     int32_t* d_lod_out, int32_t* d_scratch, pbx_stream_t stream);
+/* the same launch also copies n_dense floats d_dense_src -> d_dense_dst (label + dense block) */
+int pbx_batch_build_dense(const uint64_t* d_rec_keys, const int32_t* d_rec_off, int B, int S, uint64_t* d_keys_out,
+                          int32_t* d_lod_out, int32_t* d_scratch, const float* d_dense_src, float* d_dense_dst,
+                          int64_t n_dense, pbx_stream_t stream);
 /* Allocation-free variant of pbx_batch_build (this entry point has no counterpart in the
  * reference).  For callers that cannot allocate device memory — a feed thread running beside
  * in-flight training kernels (cudaMalloc/cudaFree synchronise the device), a process whose HBM

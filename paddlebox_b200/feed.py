@@ -136,9 +136,13 @@ class PipelinedFeed:
         tgt = self._target(hb)
         B, S = hb.batch_size, hb.num_slots
         if not (self.debug_skip_build and i >= 2):
-            N.check(N.cuda().pbx_batch_build(N.ptr(s.keys), N.ptr(s.offsets), B, S, N.ptr(tgt.keys), N.ptr(tgt.lod),
-                                             N.ptr(self.scratch), N.stream_ptr(main)), "pbx_batch_build")
-            if hb.dense is not None:
+            fold = hb.dense is not None and s.dense.is_contiguous() and tgt.dense.is_contiguous()
+            N.check(N.cuda().pbx_batch_build_dense(N.ptr(s.keys), N.ptr(s.offsets), B, S, N.ptr(tgt.keys), N.ptr(tgt.lod),
+                                                   N.ptr(self.scratch), N.ptr(s.dense) if fold else None,
+                                                   N.ptr(tgt.dense) if fold else None,
+                                                   C.c_int64(s.dense.numel() if fold else 0), N.stream_ptr(main)),
+                    "pbx_batch_build")
+            if hb.dense is not None and not fold:
                 tgt.dense.copy_(s.dense, non_blocking=True)
         s.built.record(main)
         tgt.ins_ids = hb.ins_ids
