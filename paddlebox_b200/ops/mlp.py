@@ -82,6 +82,15 @@ def cast_transpose(x: torch.Tensor, out: torch.Tensor | None, out_t: torch.Tenso
 
 
 CT_MAX = 12
+
+
+def _wgrad_splitk(B: int) -> int:
+    """Split-K factor of the grouped weight-gradient launch (the batch is the reduction axis).
+    B // 1024 keeps the whole group within one wave of two CTAs per SM for the CTR towers."""
+    env = os.environ.get("PBX_WGRAD_SPLITK")
+    if env:
+        return max(1, int(env))
+    return max(1, min(16, B // 1024))
 _SIDE_STREAMS: dict = {}
 
 
@@ -325,7 +334,7 @@ class FusedMLP(nn.Module):
             else:
                 # one grouped launch once every dZ exists (two CTAs per SM: one wave)
                 wgrads.append(gemm_problem(ws.dZt[l], ws.Ht[l], Nn, K + 1, B, out_f32=w.grad, accumulate=True,
-                                           splitk=max(1, min(16, B // 1024)), col_out=b.grad, col_split=K))
+                                           splitk=_wgrad_splitk(B), col_out=b.grad, col_split=K))
             if l > 0:
                 # dgrad fused with the ReLU mask of the previous activation
                 gemm_bf16_tn(ws.dZ[l], self._wbt[l], B, K, Nn, mask=ws.H[l], out_bf16=ws.dZ[l - 1],
