@@ -214,12 +214,19 @@ class DenseSync:
         if (self.mode != "allreduce" or not s.use_symm or engine is None or not FLAGS.pbx_fold_dense_allreduce
                 or getattr(engine, "nranks", 1) != s.nranks):
             return False
-        engine.fold_dense = (s.symm, 0, s.numel, 1.0 / s.nranks)
+        self._fold_desc = (s.symm, 0, s.numel, 1.0 / s.nranks)
+        engine.fold_dense = self._fold_desc
         engine.fold_done = False
         self.fold_engine = engine
         return True
 
     def before_forward(self) -> None:
+        if self.fold_engine is not None:
+            # several trainers may share one sparse engine (join / update models): the push of THIS
+            # step must reduce THIS trainer's gradient buffer
+            self.fold_engine.fold_dense = self._fold_desc
+            self.fold_engine.fold_done = False
+            self.fold_engine.pulls_this_step = 0
         if self.mode == "async":
             # PullDense: whole parameter vector host -> device (boxps_worker.cc:1300-1302)
             self.async_table.pull(out=self.store.flat)

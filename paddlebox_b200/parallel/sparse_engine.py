@@ -88,6 +88,7 @@ class SparseEngine:
         kernel; ``keys`` may then be a fixed-capacity buffer — this is what lets one captured
         CUDA graph serve batches of different lengths."""
         n = keys.numel()
+        self.pulls_this_step = getattr(self, "pulls_this_step", 0) + 1
         if restore is None:
             restore = torch.empty(max(n, 1), dtype=torch.int32, device=keys.device)
         N.check(N.cuda().pbx_sparse_pull_ex(self._h, N.ptr(keys), C.c_int64(n), N.ptr(n_dev), N.ptr(restore),
@@ -104,7 +105,10 @@ class SparseEngine:
         assert dout.stride(1) == 1 and dout.shape[0] == B and dout.shape[1] >= S * Eo and ld >= S * Eo \
             and dout.dtype == torch.float32
         fold = getattr(self, "fold_dense", None)
-        if fold is not None and self.nranks > 1:
+        # (only when the step has ONE pull/push pair: with several, dense gradients that depend on
+        #  a later push's inputs would not be final yet when the first push runs)
+        if fold is not None and self.nranks > 1 and getattr(self, "pulls_this_step", 1) <= 1 \
+                and not getattr(self, "fold_done", False):
             # the trainer's dense-gradient allreduce rides on this kernel's barriers
             symm, off, n, scale = fold
             N.check(N.cuda().pbx_sparse_push_dense(self._h, N.ptr(restore), C.c_int64(restore.numel()), N.ptr(dout), ld,
