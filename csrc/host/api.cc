@@ -160,6 +160,7 @@ int pbh_dataset_preload_into_memory(void* h) { return ((Dataset*)h)->preload_int
 int pbh_dataset_wait_preload_done(void* h) { return ((Dataset*)h)->wait_preload_done(); }
 int pbh_dataset_release_memory(void* h) { ((Dataset*)h)->release_memory(); return 0; }
 int pbh_dataset_local_shuffle(void* h, uint64_t seed) { ((Dataset*)h)->local_shuffle(seed); return 0; }
+int64_t pbh_dataset_merge_by_ins_id(void* h, int merge_size) { return ((Dataset*)h)->merge_by_ins_id(merge_size); }
 int pbh_dataset_slots_shuffle(void* h, const int* slots, int n, uint64_t seed) {
   return ((Dataset*)h)->slots_shuffle(std::vector<int>(slots, slots + n), seed);
 }

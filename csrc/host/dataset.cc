@@ -474,6 +474,71 @@ int Dataset::slots_shuffle(const std::vector<int>& slot_idx, uint64_t seed, bool
   return 0;
 }
 
+// Merge the records that share an instance id into one (reference MultiSlotDataset::MergeByInsId,
+// data_set.cc:1387-1581): groups whose size differs from merge_size (> 0) are dropped; a sparse
+// slot may carry values in at most one record of a group (else the group is dropped as
+// conflicting); of a float slot the first non-empty, non-zero copy wins.  Returns the number of
+// dropped instances.
+int64_t Dataset::merge_by_ins_id(int merge_size) {
+  std::stable_sort(records_.begin(), records_.end(),
+                   [](const SlotRecord* a, const SlotRecord* b) { return a->ins_id < b->ins_id; });
+  std::vector<SlotRecord*> out, dropped;
+  int64_t n_drop = 0;
+  for (size_t i = 0; i < records_.size();) {
+    size_t j = i + 1;
+    while (j < records_.size() && records_[j]->ins_id == records_[i]->ins_id) ++j;
+    const size_t g = j - i;
+    bool keep = !(merge_size > 0 && (int)g != merge_size);
+    if (keep && g > 1) {
+      SlotRecord* m = records_[i];
+      std::vector<std::vector<uint64_t>> u(n_used_u64_);
+      std::vector<std::vector<float>> f(n_used_f_);
+      for (size_t k = i; k < j && keep; ++k) {
+        const SlotRecord* r = records_[k];
+        for (int p = 0; p < n_used_u64_ && p + 1 < (int)r->u64_offs.size(); ++p) {
+          const uint32_t a = r->u64_offs[p], e = r->u64_offs[p + 1];
+          if (a == e) continue;
+          if (!u[p].empty()) { keep = false; break; }          // conflicting sparse slot
+          u[p].assign(r->u64_vals.begin() + a, r->u64_vals.begin() + e);
+        }
+        for (int p = 0; p < n_used_f_ && p + 1 < (int)r->f_offs.size(); ++p) {
+          const uint32_t a = r->f_offs[p], e = r->f_offs[p + 1];
+          if (a == e || !f[p].empty()) continue;
+          bool nonzero = false;
+          for (uint32_t q = a; q < e; ++q) nonzero |= r->f_vals[q] != 0.f;
+          if (nonzero || k + 1 == j) f[p].assign(r->f_vals.begin() + a, r->f_vals.begin() + e);
+        }
+      }
+      if (keep) {
+        m->u64_vals.clear();
+        m->u64_offs.assign(n_used_u64_ + 1, 0);
+        for (int p = 0; p < n_used_u64_; ++p) {
+          m->u64_vals.insert(m->u64_vals.end(), u[p].begin(), u[p].end());
+          m->u64_offs[p + 1] = (uint32_t)m->u64_vals.size();
+        }
+        m->f_vals.clear();
+        m->f_offs.assign(n_used_f_ + 1, 0);
+        for (int p = 0; p < n_used_f_; ++p) {
+          m->f_vals.insert(m->f_vals.end(), f[p].begin(), f[p].end());
+          m->f_offs[p + 1] = (uint32_t)m->f_vals.size();
+        }
+        out.push_back(m);
+        for (size_t k = i + 1; k < j; ++k) dropped.push_back(records_[k]);
+      }
+    } else if (keep) {
+      out.push_back(records_[i]);
+    }
+    if (!keep) {
+      n_drop += (int64_t)g;
+      for (size_t k = i; k < j; ++k) dropped.push_back(records_[k]);
+    }
+    i = j;
+  }
+  records_.swap(out);
+  pool_.put(dropped);
+  return n_drop;
+}
+
 int Dataset::prepare_train(int nworkers, bool shuffle, uint64_t seed, int64_t min_batches) {
   PBH_REQUIRE(nworkers >= 1, "nworkers must be >= 1");
   if (enable_pv_merge) {

@@ -103,6 +103,7 @@ class Dataset {
   int wait_preload_done();
   void release_memory();
   void local_shuffle(uint64_t seed);
+  int64_t merge_by_ins_id(int merge_size);   // merge records sharing an ins_id; returns dropped instances
   int slots_shuffle(const std::vector<int>& slot_idx, uint64_t seed, bool inverse = false);  // AUC runner: permute slots across records
   int prepare_train(int nworkers, bool shuffle, uint64_t seed, int64_t min_batches);
   int64_t num_records() const { return (int64_t)records_.size(); }

@@ -28,6 +28,9 @@ int pbh_dataset_preload_into_memory(void* ds);
 int pbh_dataset_wait_preload_done(void* ds);
 int pbh_dataset_release_memory(void* ds);
 int pbh_dataset_local_shuffle(void* ds, uint64_t seed);
+/* merge the loaded records that share an ins_id (merge_size > 0: groups of another size are dropped;
+ * groups with a sparse slot filled twice are dropped); returns the number of dropped instances */
+int64_t pbh_dataset_merge_by_ins_id(void* ds, int merge_size);
 int pbh_dataset_slots_shuffle(void* ds, const int* slots, int n, uint64_t seed);
 /* undoes pbh_dataset_slots_shuffle called with the same slots and seed */
 int pbh_dataset_slots_shuffle_back(void* ds, const int* slots, int n, uint64_t seed);

@@ -187,8 +187,14 @@ class InMemoryDataset(DatasetBase):
         self._native.set("enable_pv_merge", int(v))
 
     def set_merge_by_lineid(self, merge_size: int = 2):
+        """Instances sharing an ins_id are merged into one after loading (``MergeByInsId``,
+        data_set.cc:1387-1581); needs ``set_parse_ins_id(True)``."""
         self.merge_by_lineid = True
         self.merge_size = merge_size
+
+    def merge_by_ins_id(self) -> int:
+        """Apply the merge now; returns the number of dropped instances."""
+        return self._native.merge_by_ins_id(getattr(self, "merge_size", 0))
 
     def set_sample_rate(self, rate: float):
         self._native.set("sample_rate", float(rate))
@@ -229,6 +235,8 @@ class InMemoryDataset(DatasetBase):
     # pass data ---------------------------------------------------------------------------------
     def load_into_memory(self):
         self._native.load_into_memory()
+        if self.merge_by_lineid:
+            self.merge_by_ins_id()
         monitor.stat_set("STAT_total_feasign_num_in_mem", self._native.total_feasigns())
 
     def preload_into_memory(self, thread_num: int | None = None):
@@ -238,6 +246,8 @@ class InMemoryDataset(DatasetBase):
 
     def wait_preload_done(self):
         self._native.wait_preload_done()
+        if self.merge_by_lineid:
+            self.merge_by_ins_id()
         monitor.stat_set("STAT_total_feasign_num_in_mem", self._native.total_feasigns())
 
     def release_memory(self):

@@ -298,6 +298,11 @@ class NativeDataset:
         n = len(slot_indices)
         N.hcheck(N.host().pbh_dataset_slots_shuffle(self._h, (C.c_int * n)(*slot_indices), n, C.c_uint64(seed)))
 
+    def merge_by_ins_id(self, merge_size: int = 0) -> int:
+        fn = N.host().pbh_dataset_merge_by_ins_id
+        fn.restype = C.c_int64
+        return int(fn(self._h, int(merge_size)))
+
     def slots_shuffle_back(self, slot_indices: Sequence[int], seed: int = 0):
         n = len(slot_indices)
         N.hcheck(N.host().pbh_dataset_slots_shuffle_back(self._h, (C.c_int * n)(*slot_indices), n, C.c_uint64(seed)))

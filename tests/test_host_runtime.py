@@ -320,3 +320,34 @@ def test_pv_batches_carry_rank_offset(tmp_path):
     # ranks outside [1, max_rank] are ignored
     ro = build_rank_offset(torch.tensor([5, 5, 5]), torch.tensor([1, 9, 2]), 3)
     assert ro[1].tolist() == [-1] * 7 and ro[0].tolist() == [1, 1, 0, 2, 2, -1, -1]
+
+
+def test_merge_by_ins_id(tmp_path):
+    """Two half-instances with the same ins_id (disjoint slots) become one; groups of the wrong
+    size and groups that fill one sparse slot twice are dropped."""
+    import torch
+    from paddlebox_b200.data_generator import format_instance
+    from paddlebox_b200.dataset import DatasetFactory, dense_slot, sparse_slot
+    lines = [
+        format_instance([[1.0], [11], [0]], ins_id="a"),         # a: slot s0 here (a zero feasign = empty slot) ...
+        format_instance([[0.0], [0], [21, 22]], ins_id="a"),     # ... slot s1 there -> merged
+        format_instance([[1.0], [31], [32]], ins_id="b"),        # b: single record -> group size 1 != 2: dropped
+        format_instance([[0.0], [41], [0]], ins_id="c"),
+        format_instance([[1.0], [42], [43]], ins_id="c"),        # c: s0 filled twice -> conflict: dropped
+    ]
+    path = tmp_path / "part-0"
+    path.write_text("\n".join(lines) + "\n")
+    ds = DatasetFactory().create_dataset("InMemoryDataset")
+    ds.set_use_var([dense_slot("label", 1), sparse_slot("s0"), sparse_slot("s1")])
+    ds.set_batch_size(4)
+    ds.set_thread(1)
+    ds.set_parse_ins_id(True)
+    ds.set_merge_by_lineid(2)
+    ds.set_filelist([str(path)])
+    ds.load_into_memory()
+    assert ds.get_memory_data_size() == 1
+    ds.prepare_train(1)
+    (b,) = list(ds.batches(device=torch.device("cpu"), with_ins_id=True))
+    assert b.batch_size == 1 and b.ins_ids == ["a"]
+    assert sorted(b.keys.tolist()) == [11, 21, 22]
+    assert float(b.dense[0, 0]) == 1.0           # the first non-zero label copy wins
