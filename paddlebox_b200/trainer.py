@@ -110,14 +110,17 @@ class CTRTrainer:
             g = torch.cuda.CUDAGraph()
             # thread_local: a loader thread that pins host memory while we capture must not
             # invalidate the capture
-            with torch.cuda.graph(g, capture_error_mode="thread_local"):
+            # (captured on the stream the warm-up ran on: tensors cached during warm-up — the root
+            #  gradient, workspaces — then carry no dependency on a stream outside the capture)
+            with torch.cuda.graph(g, stream=side, capture_error_mode="thread_local"):
                 loss = self._eager_step(static)
             self._graph, self._graph_loss = g, loss
             torch.cuda.synchronize(dev)
             return True
         except Exception as e:  # capture unsupported (e.g. cooperative launch in capture): stay eager
+            import traceback
             self._graph = None
-            self._graph_error = repr(e)
+            self._graph_error = repr(e) + "\n" + traceback.format_exc()
             torch.cuda.synchronize(dev)
             return False
 
