@@ -177,6 +177,9 @@ def main():
         return 2
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    # one non-default stream for the whole job: eager steps, graph warm-up, capture and replay all
+    # see the same stream (see CTRTrainer.enable_cuda_graph)
+    torch.cuda.set_stream(torch.cuda.Stream(device=dev))
     import torch.distributed as dist
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")

@@ -99,7 +99,13 @@ class CTRTrainer:
         self._static = static
         self._copy_into_static(example_batch)
         try:
-            side = torch.cuda.Stream(device=dev)
+            # Autograd runs a parameter's gradient accumulation on the stream that was current when
+            # the parameter was FIRST used; if that was the default stream, a capture on any other
+            # stream fails ("dependency created on uncaptured work in another stream").  A caller that
+            # trains on a stream of its own from the start (torch.cuda.set_stream) gets warm-up and
+            # capture on that same stream.
+            cur = torch.cuda.current_stream(dev)
+            side = cur if cur != torch.cuda.default_stream(dev) else torch.cuda.Stream(device=dev)
             side.wait_stream(torch.cuda.current_stream(dev))
             with torch.cuda.stream(side):
                 for _ in range(max(1, warmup)):
