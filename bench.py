@@ -289,7 +289,7 @@ def main():
     dev_ms = sum(a.elapsed_time(b) for a, b in evs)
     box.engine.check_status()
     sparse_phases = box.engine.phase_times()      # last timed step, this rank
-    loss_val = float(loss)
+    loss_val = float(loss.detach())
 
     if args.timeline and rank == 0:
         # diagnosis only (never a timing of record): kernel start/duration inside the replayed graph
