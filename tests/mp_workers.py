@@ -234,3 +234,34 @@ def cpu_global_shuffle_and_cluster(rank, world):
     c.barrier()
     return dict(before=n_before, after=n_after, total_before=total_before, total_after=total_after,
                 biggest=biggest, sums=sums.tolist(), ranks=ranks)
+
+
+def cpu_collective_ops(rank, world):
+    """c_allreduce_xsum / c_mixallgather (modes 0, 1, 2) / c_broadcast on CPU tensors over gloo."""
+    from paddlebox_b200.parallel import collective as Cc
+    a = torch.full((5,), float(rank + 1))
+    b = torch.arange(6, dtype=torch.float32).reshape(2, 3) * (rank + 1)
+    Cc.c_allreduce_xsum([a, b], scale=0.5)
+    tot = sum(range(1, world + 1))
+    ok = torch.allclose(a, torch.full((5,), 0.5 * tot)) and \
+        torch.allclose(b, torch.arange(6, dtype=torch.float32).reshape(2, 3) * tot * 0.5)
+    g = torch.full((7,), float(rank + 1))
+    Cc.c_mixallgather([g], mode=0)                     # mean
+    ok = ok and torch.allclose(g, torch.full((7,), tot / world))
+    g1 = torch.full((7,), float(rank + 1))
+    Cc.c_mixallgather([g1], mode=1)                    # reduce-scatter + all-gather == mean
+    ok = ok and torch.allclose(g1, torch.full((7,), tot / world))
+    # mode 2: every rank contributes its own contiguous shard of the tensor
+    n = 9
+    chunk = (n + world - 1) // world
+    full = torch.arange(n, dtype=torch.float32)
+    mine = torch.zeros(n)
+    lo, hi = min(n, rank * chunk), min(n, rank * chunk + chunk)
+    mine[lo:hi] = full[lo:hi]
+    Cc.c_mixallgather([mine], mode=2)
+    ok = ok and torch.equal(mine, full)
+    w = torch.full((3,), float(rank))
+    Cc.c_broadcast([w], root=1)
+    ok = ok and torch.equal(w, torch.full((3,), 1.0))
+    Cc.barrier()
+    return bool(ok)

@@ -56,6 +56,10 @@ def test_global_shuffle_and_cluster_two_ranks_gloo():
     assert outs[0]["sums"] == [3.0, 2.0] and outs[1]["ranks"] == [0, 1]
 
 
+def test_collective_ops_two_ranks_gloo():
+    assert all(_spawn(W.cpu_collective_ops, 2, "gloo"))
+
+
 def _ngpu():
     return torch.cuda.device_count() if torch.cuda.is_available() else 0
 
