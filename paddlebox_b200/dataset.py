@@ -438,6 +438,35 @@ class InputTableDataset(PadBoxSlotDataset):
     def set_index_filelist(self, filelist: Sequence[str]):
         self.index_filelist = list(filelist)
 
+    def set_input_table_dim(self, dim: int):
+        self.input_table_dim = int(dim)
+
+    @property
+    def input_table(self):
+        """The ``InputTable`` of the current BoxWrapper (created on first use)."""
+        from .side_tables import InputTable
+        box = self.boxps
+        if getattr(box, "input_table", None) is None:
+            box.input_table = InputTable(getattr(self, "input_table_dim", 1))
+        return box.input_table
+
+    def load_index_into_memory(self) -> int:
+        """Read the index files (``key<TAB>v1 v2 ...``) into the input table
+        (``InputTableDataset::LoadIndexIntoMemory``, data_set.cc:2830-2858; feed
+        ``InputIndexDataFeed``, data_feed.cc:4574-4633).  Returns the number of rows added."""
+        tab = self.input_table
+        return sum(tab.load_index_file(f) for f in getattr(self, "index_filelist", []))
+
+    def index_offsets(self, keys: Sequence[str]) -> torch.Tensor:
+        """Row offsets of string keys (0 = miss): what a parser plugin obtains through the
+        reference's ``GetOffsetFunc`` callback and stores in an id slot for ``lookup_input``."""
+        tab = self.input_table
+        return torch.tensor([tab.get_index_offset(k) for k in keys], dtype=torch.int64)
+
+    def load_into_memory(self):
+        self.load_index_into_memory()
+        super().load_into_memory()
+
 
 class DatasetFactory:
     """``DatasetFactory().create_dataset("PadBoxSlotDataset")`` (dataset.py:30-63)."""

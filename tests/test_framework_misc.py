@@ -248,3 +248,31 @@ def test_data_norm_module_updates_summaries():
     assert torch.allclose(dn.batch_size, torch.full((3,), 1e4 * 0.5 + 1))
     assert torch.allclose(dn.batch_sum, torch.tensor([2., 2., 2.]))
     assert torch.allclose(x.grad, torch.ones(2, 3) * torch.sqrt(torch.tensor(1e4 / 1e4)))
+
+
+def test_input_table_dataset_loads_index_files(tmp_path):
+    import torch
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    from paddlebox_b200.dataset import DatasetFactory
+    from tests.util_data import slot_vars, write_files
+    BoxWrapper.reset_instance()
+    box = BoxWrapper.set_instance(embedx_dim=8, device=torch.device("cpu"), rank=0, world_size=1)
+    box.initialize_gpu_and_load_model({})
+    try:
+        idx = tmp_path / "index-0"
+        idx.write_text("query_a\t0.5 1.5 2.5\nquery_b\t1 2 3\nbad line\n")
+        ds = DatasetFactory().create_dataset("InputTableDataset")
+        ds.set_use_var(slot_vars(3, 2))
+        ds.set_batch_size(8)
+        ds.set_thread(1)
+        ds.set_input_table_dim(3)
+        ds.set_index_filelist([str(idx)])
+        ds.set_filelist(write_files(str(tmp_path), n_files=1, lines_per_file=16, n_sparse=3, n_dense=2, key_space=20))
+        ds.load_into_memory()
+        assert ds.input_table.size() == 2 and ds.get_memory_data_size() == 16
+        off = ds.index_offsets(["query_b", "nope", "query_a"])
+        assert off.tolist() == [2, 0, 1] and ds.input_table.miss == 1
+        rows = ds.input_table.lookup_input(off)
+        assert torch.allclose(rows, torch.tensor([[1., 2., 3.], [0., 0., 0.], [0.5, 1.5, 2.5]]))
+    finally:
+        BoxWrapper.reset_instance()
