@@ -276,3 +276,25 @@ def test_input_table_dataset_loads_index_files(tmp_path):
         assert torch.allclose(rows, torch.tensor([[1., 2., 3.], [0., 0., 0.], [0.5, 1.5, 2.5]]))
     finally:
         BoxWrapper.reset_instance()
+
+
+def test_queue_dataset_streams_in_file_order(tmp_path):
+    import torch
+    from paddlebox_b200.dataset import DatasetFactory
+    from tests.util_data import slot_vars, write_files
+    ds = DatasetFactory().create_dataset("QueueDataset")
+    ds.set_use_var(slot_vars(2, 1))
+    ds.set_batch_size(5)
+    ds.set_thread(1)
+    ds.set_merge_thread_num(1)
+    files = write_files(str(tmp_path), n_files=1, lines_per_file=20, n_sparse=2, n_dense=1, key_space=1000)
+    ds.set_filelist(files)
+    ds.load_into_memory()
+    with pytest.raises(NotImplementedError):
+        ds.local_shuffle()
+    ds.prepare_train(1)
+    labels = torch.cat([b.dense[:, 0] for b in ds.batches(device=torch.device("cpu"))])
+    # file order is preserved: the labels come back in the order they were written
+    want = [float(line.split()[1]) for line in open(files[0])]
+    assert labels.tolist() == want
+    assert ds.unique_keys().size == 0            # a streaming dataset does not collect pass keys
