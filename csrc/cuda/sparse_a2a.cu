@@ -100,6 +100,7 @@ __device__ __forceinline__ void xbarrier(cg::grid_group& grid, const PbxSparseDe
   if (threadIdx.x < c.nranks) {
     const uint64_t t0 = pbx_globaltimer();
     while (pbx_ld_acquire_sys(c.flags[c.rank] + threadIdx.x) < target) {
+      __nanosleep(32);   // 148 CTAs x R pollers: back off so the polls do not crowd the memory system
       if (pbx_globaltimer() - t0 > 20000000000ull) {  // 20 s: a peer died; fail loudly, do not hang
         atomicExch(c.status, 2);
         break;
