@@ -222,7 +222,6 @@ int pbx_table_create(void** out, uint64_t capacity, int embedx_dim, int optimize
   t->view.seed = seed;
   t->view.L = pbx_make_layout(embedx_dim, optimizer);
   t->view.cfg = *cfg;
-  t->view.dbg = getenv("PBX_DBG") ? atoi(getenv("PBX_DBG")) : 0;
   PBX_CUDA_CHECK(cudaMalloc(&t->view.keys, capacity * sizeof(uint64_t)));
   PBX_CUDA_CHECK(cudaMalloc(&t->view.vals, capacity * (uint64_t)t->view.L.stride * sizeof(float)));
   PBX_CUDA_CHECK(cudaMalloc(&t->view.dirty, capacity));

@@ -18,7 +18,6 @@ struct PbxTableView {
   PbxRowLayout L;
   PbxSparseOptConfig cfg;
   int test_mode;      // 1: pushes are ignored (reference SetTestMode)
-  int dbg;            // PBX_DBG env: perf experiments only (bit0 no dirty mark, bit1 no row stores, bit2 no embedx loop)
 };
 
 __device__ __forceinline__ uint32_t pbx_dev_find(const PbxTableView& t, uint64_t key) {
@@ -230,7 +229,7 @@ __device__ __forceinline__ void pbx_apply_push_adagrad_stream(const PbxTableView
       rA.y = pbx_uniform01(key, D - 2, t.seed) * rg;
       rA.z = pbx_uniform01(key, D - 1, t.seed) * rg;
     }
-  } else if (!(t.dbg & 4)) {
+  } else {
     const float ratio = c.mf_learning_rate * sqrtf(c.mf_initial_g2sum / (c.mf_initial_g2sum + rC.x));
     const float lo = c.mf_min_bound, hi = c.mf_max_bound;
     float add = 0.f;
@@ -253,13 +252,11 @@ __device__ __forceinline__ void pbx_apply_push_adagrad_stream(const PbxTableView
     sg = pk.w * inv; rA.z = fminf(fmaxf(rA.z + sg * ratio, lo), hi); add += sg * sg;
     rC.x += add / (float)D;
   }
-  if (!(t.dbg & 2)) {
-    rowv[0] = r0;
-    rowv[q] = rA;
-    rowv[q + 1] = rB;
-    rowv[q + 2] = rC;
-  }
-  if (!(t.dbg & 1) && t.dirty) t.dirty[slot_idx] = 1;
+  rowv[0] = r0;
+  rowv[q] = rA;
+  rowv[q + 1] = rB;
+  rowv[q + 2] = rC;
+  if (t.dirty) t.dirty[slot_idx] = 1;
 }
 
 // dispatch: streaming vector path for Adagrad with D % 4 == 0 (D >= 4), generic scalar otherwise
