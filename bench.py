@@ -78,6 +78,8 @@ def reference_arm(args):
     # fetched from an internal host; /root/reference has neither setup.py nor pyproject.toml
     # (pip: "Directory '/root/reference' is not installable") and its CMake build needs ~40
     # network-fetched third-party projects.  See DESIGN.md "Reference arm".
+    if int(os.environ.get("RANK", "0")) != 0:      # under torchrun: one line, from rank 0
+        return 0
     print(json.dumps({"impl": "reference",
                       "unavailable": "reference is not pip-installable offline (no setup.py/pyproject.toml; "
                                      "BoxPS core libbox_ps.so is a closed binary; CMake build needs network)"}))
