@@ -31,13 +31,30 @@ bool ThreadPool::set_cpu_affinity(std::thread& t, int core) {
 }
 
 // ---------------------------------------------------------------- KeyAgent
+// Keys are bucketed into thread-local per-shard buffers; a buffer goes to its shard (one lock) only
+// when it holds a few thousand keys, so the per-key cost is a hash and a push_back.  Every thread
+// that added keys must call flush_local() before the shards are read (merge_loop does).
+static thread_local std::vector<std::vector<uint64_t>> tl_agent_local;
+
 void KeyAgent::add_keys(const uint64_t* keys, size_t n) {
   const size_t S = shards_.size();
-  // bucket locally first so that each shard lock is taken once per call
-  thread_local std::vector<std::vector<uint64_t>> local;
+  auto& local = tl_agent_local;
   if (local.size() != S) local.assign(S, {});
-  for (size_t i = 0; i < n; ++i) local[mix64(keys[i]) % S].push_back(keys[i]);
-  for (size_t s = 0; s < S; ++s) {
+  for (size_t i = 0; i < n; ++i) {
+    auto& b = local[mix64(keys[i]) % S];
+    b.push_back(keys[i]);
+    if (b.size() >= 4096) {
+      const size_t s = (size_t)(&b - &local[0]);
+      std::lock_guard<std::mutex> g(mu_[s]);
+      shards_[s].insert(shards_[s].end(), b.begin(), b.end());
+      b.clear();
+    }
+  }
+}
+
+void KeyAgent::flush_local() {
+  auto& local = tl_agent_local;
+  for (size_t s = 0; s < local.size() && s < shards_.size(); ++s) {
     if (local[s].empty()) continue;
     std::lock_guard<std::mutex> g(mu_[s]);
     shards_[s].insert(shards_[s].end(), local[s].begin(), local[s].end());
@@ -356,6 +373,7 @@ void Dataset::merge_loop() {
       mine.clear();
     }
   }
+  agent_.flush_local();
   std::lock_guard<std::mutex> g(rec_mu_);
   records_.insert(records_.end(), mine.begin(), mine.end());
 }
@@ -742,6 +760,7 @@ int Dataset::load_archive(const std::string& path) {
   if (collect_keys) {
     // several archives may be loaded into one pass (global shuffle): keep the union of their keys
     agent_.add_keys(unique_keys_.data(), unique_keys_.size());
+    agent_.flush_local();
     ThreadPool pool(std::max(1, merge_thread_num));
     agent_.finalize(&pool, &unique_keys_);
     agent_.clear();

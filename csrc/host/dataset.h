@@ -67,7 +67,8 @@ class KeyAgent {
  public:
   explicit KeyAgent(int shards = 64) : shards_(shards), mu_(shards) {}
   void add_keys(const uint64_t* keys, size_t n);
-  void add_key(uint64_t k) { add_keys(&k, 1); }
+  void add_key(uint64_t k) { add_keys(&k, 1); flush_local(); }
+  void flush_local();   // publish this thread's buffered keys (call before finalize)
   // sort+unique every shard (parallel) and concatenate
   void finalize(ThreadPool* pool, std::vector<uint64_t>* out);
   void clear() { for (auto& s : shards_) { s.clear(); s.shrink_to_fit(); } }

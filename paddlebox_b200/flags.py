@@ -89,6 +89,7 @@ _d("check_nan_inf", False, "abort + dump on NaN/Inf in a batch (boxps_worker.cc:
 _d("enable_debug_print_metrics_info", False, "verbose AUC computation (metrics.cc:29-31)")
 # --- this framework -------------------------------------------------------------------
 _d("pbx_use_cuda_graph", True, "capture the training step in a CUDA graph when shapes allow")
+_d("pbx_pack_threads", 4, "background threads packing mini-batches into staging buffers (per loader)")
 _d("pbx_overlap_wgrad", False, "weight-gradient GEMMs on a side stream, concurrently with the dgrad chain (measured: no gain over the grouped launch)")
 _d("pbx_fold_dense_allreduce", True, "data-parallel dense-gradient allreduce rides on the sparse push kernel's barriers")
 _d("pbx_sparse_cap_factor", 2.0, "mailbox capacity = factor * max_keys / nranks")
