@@ -136,6 +136,8 @@ int pbh_dataset_set_int(void* h, const char* key, int64_t v) {
   else if (k == "parse_logkey") d->parse_logkey = v != 0;
   else if (k == "enable_pv_merge") d->enable_pv_merge = v != 0;
   else if (k == "collect_keys") d->collect_keys = v != 0;
+  else if (k == "compact_batches") d->compact_batches = (int)v;
+  else if (k == "compact_limit_mb") d->compact_limit_mb = (int64_t)v;
   else if (k == "rank") d->rank = (int)v;
   else if (k == "world") d->world = (int)v;
   else { pbh::set_error("unknown dataset option %s", key); return -1; }

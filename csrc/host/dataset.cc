@@ -379,6 +379,7 @@ void Dataset::merge_loop() {
 }
 
 int Dataset::load_into_memory() {
+  drop_arena();
   PBH_REQUIRE(!slots.empty(), "dataset has no slots (call set_use_var first)");
   if (slot_to_sparse_.size() != slots.size()) {
     int rc = finalize_slots();
@@ -434,6 +435,7 @@ int Dataset::wait_preload_done() {
 }
 
 void Dataset::release_memory() {
+  drop_arena();
   pool_.put(records_);
   records_.shrink_to_fit();
   worker_batches_.clear();
@@ -445,6 +447,7 @@ void Dataset::release_memory() {
 }
 
 void Dataset::local_shuffle(uint64_t seed) {
+  drop_arena();
   std::mt19937_64 rng(seed);
   std::shuffle(records_.begin(), records_.end(), rng);
 }
@@ -453,6 +456,8 @@ void Dataset::local_shuffle(uint64_t seed) {
 // slot in place, to measure how much the model relies on those slots
 // (reference RecordReplace / slots_shuffle, data_feed.h:1772-1962, box_wrapper.cc:212-368).
 int Dataset::slots_shuffle(const std::vector<int>& slot_idx, uint64_t seed, bool inverse) {
+  const bool had_arena = arena_ok_;
+  drop_arena();
   const size_t n = records_.size();
   if (n < 2) return 0;
   std::vector<size_t> perm(n);
@@ -489,6 +494,7 @@ int Dataset::slots_shuffle(const std::vector<int>& slot_idx, uint64_t seed, bool
     r->u64_vals.swap(nv);
     r->u64_offs.swap(no);
   }
+  if (had_arena) build_arena();   // same order, same batches: only the values changed
   return 0;
 }
 
@@ -498,6 +504,7 @@ int Dataset::slots_shuffle(const std::vector<int>& slot_idx, uint64_t seed, bool
 // conflicting); of a float slot the first non-empty, non-zero copy wins.  Returns the number of
 // dropped instances.
 int64_t Dataset::merge_by_ins_id(int merge_size) {
+  drop_arena();
   std::stable_sort(records_.begin(), records_.end(),
                    [](const SlotRecord* a, const SlotRecord* b) { return a->ins_id < b->ins_id; });
   std::vector<SlotRecord*> out, dropped;
@@ -557,6 +564,45 @@ int64_t Dataset::merge_by_ins_id(int merge_size) {
   return n_drop;
 }
 
+void Dataset::drop_arena() {
+  arena_ok_ = false;
+  std::vector<uint64_t>().swap(ar_keys_);
+  std::vector<int64_t>().swap(ar_koff_);
+  std::vector<uint32_t>().swap(ar_soff_);
+  std::vector<float>().swap(ar_dense_);
+}
+
+void Dataset::build_arena() {
+  drop_arena();
+  const size_t n = records_.size();
+  if (compact_batches == 0 || n == 0) return;
+  const int S = n_used_u64_;
+  ar_koff_.assign(n + 1, 0);
+  for (size_t i = 0; i < n; ++i) ar_koff_[i + 1] = ar_koff_[i] + (int64_t)records_[i]->u64_vals.size();
+  const int64_t bytes = ar_koff_[n] * 8 + (int64_t)n * ((S + 1) * 4 + dense_dim_ * 4);
+  if (compact_batches == 1 && bytes > compact_limit_mb * (1ll << 20)) { drop_arena(); return; }
+  ar_keys_.resize((size_t)ar_koff_[n]);
+  ar_soff_.resize(n * (size_t)(S + 1));
+  ar_dense_.assign(n * (size_t)dense_dim_, 0.f);
+  ThreadPool pool(std::max(1, merge_thread_num));
+  pool.parallel_range(n, [&](size_t b, size_t e, int) {
+    for (size_t i = b; i < e; ++i) {
+      const SlotRecord* rec = records_[i];
+      if (!rec->u64_vals.empty())
+        memcpy(ar_keys_.data() + ar_koff_[i], rec->u64_vals.data(), rec->u64_vals.size() * sizeof(uint64_t));
+      uint32_t* so = ar_soff_.data() + i * (size_t)(S + 1);
+      for (int s = 0; s <= S; ++s) so[s] = s < (int)rec->u64_offs.size() ? rec->u64_offs[s] : (uint32_t)rec->u64_vals.size();
+      float* d = ar_dense_.data() + i * (size_t)dense_dim_;
+      for (int f = 0; f < n_used_f_ && f + 1 < (int)rec->f_offs.size(); ++f) {
+        const uint32_t a = rec->f_offs[f], en = rec->f_offs[f + 1];
+        const int dim = float_dim_[f];
+        for (int j = 0; j < dim; ++j) d[float_off_[f] + j] = (a + j < en) ? rec->f_vals[a + j] : 0.f;
+      }
+    }
+  });
+  arena_ok_ = true;
+}
+
 int Dataset::prepare_train(int nworkers, bool shuffle, uint64_t seed, int64_t min_batches) {
   PBH_REQUIRE(nworkers >= 1, "nworkers must be >= 1");
   if (enable_pv_merge) {
@@ -588,6 +634,7 @@ int Dataset::prepare_train(int nworkers, bool shuffle, uint64_t seed, int64_t mi
       }
     }
   }
+  build_arena();
   return 0;
 }
 
@@ -596,7 +643,8 @@ int Dataset::batch_shape(int worker, int64_t b, int* B, int64_t* n_keys) const {
                   b < (int64_t)worker_batches_[worker].size(), "batch (%d, %lld) out of range", worker, (long long)b);
   const BatchRange& r = worker_batches_[worker][b];
   int64_t nk = 0;
-  for (int i = 0; i < r.len; ++i) nk += (int64_t)records_[r.start + i]->u64_vals.size();
+  if (arena_ok_) nk = ar_koff_[r.start + r.len] - ar_koff_[r.start];
+  else for (int i = 0; i < r.len; ++i) nk += (int64_t)records_[r.start + i]->u64_vals.size();
   *B = r.len;
   *n_keys = nk;
   return 0;
@@ -607,6 +655,21 @@ int Dataset::pack_batch(int worker, int64_t b, uint64_t* keys, int32_t* off, flo
                   b < (int64_t)worker_batches_[worker].size(), "batch (%d, %lld) out of range", worker, (long long)b);
   const BatchRange& r = worker_batches_[worker][b];
   const int B = r.len, S = n_used_u64_;
+  if (arena_ok_ && !slot_major) {
+    // compact arena: three contiguous copies
+    const int64_t k0 = ar_koff_[r.start];
+    memcpy(keys, ar_keys_.data() + k0, (size_t)(ar_koff_[r.start + B] - k0) * sizeof(uint64_t));
+    const uint32_t* so = ar_soff_.data() + (size_t)r.start * (S + 1);
+    for (int i = 0; i < B; ++i) {
+      const int32_t base = (int32_t)(ar_koff_[r.start + i] - k0);
+      int32_t* o = off + (int64_t)i * (S + 1);
+      const uint32_t* si = so + (size_t)i * (S + 1);
+      for (int s = 0; s <= S; ++s) o[s] = base + (int32_t)si[s];
+    }
+    if (dense && dense_dim_ > 0)
+      memcpy(dense, ar_dense_.data() + (size_t)r.start * dense_dim_, (size_t)B * dense_dim_ * sizeof(float));
+    return 0;
+  }
   if (!slot_major) {
     int64_t cur = 0;
     for (int i = 0; i < B; ++i) {
@@ -728,6 +791,7 @@ int Dataset::save_partitioned(const std::string& prefix, int nparts, int mode, u
 }
 
 int Dataset::load_archive(const std::string& path) {
+  drop_arena();
   FILE* fp = fopen(path.c_str(), "rb");
   PBH_REQUIRE(fp != nullptr, "cannot open %s", path.c_str());
   auto rd = [&](void* p, size_t n) { return fread(p, 1, n, fp) == n; };

@@ -95,6 +95,8 @@ class Dataset {
   float sample_rate = 1.0f;
   bool enable_pv_merge = false;
   bool collect_keys = true;
+  int compact_batches = 1;         // 1: build the compact arena when it is below compact_limit_mb; 2: always; 0: never
+  int64_t compact_limit_mb = 16384;
   int rank = 0, world = 1;         // file round-robin across nodes (data_set.cc:1963-1975)
 
   int finalize_slots();            // builds the used-slot index maps
@@ -141,6 +143,16 @@ class Dataset {
   int dense_dim_ = 0;
   int n_used_u64_ = 0, n_used_f_ = 0;
   std::vector<SlotRecord*> records_;
+  // Compact copy of the pass in records_ order, built by prepare_train (compact_batches): packing
+  // a batch is then three contiguous copies instead of one heap record chase per instance.
+  // Dropped (arena_ok_ = false) by anything that reorders or edits records_.
+  bool arena_ok_ = false;
+  std::vector<uint64_t> ar_keys_;    // all feasigns, record after record
+  std::vector<int64_t> ar_koff_;     // [n + 1] first feasign of every record
+  std::vector<uint32_t> ar_soff_;    // [n * (S + 1)] slot offsets inside the record
+  std::vector<float> ar_dense_;      // [n * dense_dim] densified float slots
+  void build_arena();
+  void drop_arena();
   std::mutex rec_mu_;
   RecordPool pool_;
   Channel<std::vector<SlotRecord*>> chan_;

@@ -221,6 +221,13 @@ class InMemoryDataset(DatasetBase):
     def set_ads_offset(self, name: str):
         self.ads_offset_name = name
 
+    def set_compact_batches(self, mode: int = 1, limit_mb: int | None = None):
+        """Compact copy of the pass built by ``prepare_train`` so that packing a batch is three
+        contiguous copies (0 never, 1 when it fits ``limit_mb`` [default 16 GB], 2 always)."""
+        self._native.set("compact_batches", int(mode))
+        if limit_mb is not None:
+            self._native.set("compact_limit_mb", int(limit_mb))
+
     def set_merge_thread_num(self, n: int):
         self._native.set("merge_thread_num", int(n))
 

@@ -351,3 +351,42 @@ def test_merge_by_ins_id(tmp_path):
     assert b.batch_size == 1 and b.ins_ids == ["a"]
     assert sorted(b.keys.tolist()) == [11, 21, 22]
     assert float(b.dense[0, 0]) == 1.0           # the first non-zero label copy wins
+
+
+def test_compact_arena_pack_matches_record_chase(tmp_path):
+    """Record-major packing from the compact arena equals packing from the heap records, also
+    after a slot shuffle (arena rebuilt) and with the arena switched off."""
+    import numpy as np
+    from paddlebox_b200.dataset import DatasetFactory
+    from tests.util_data import slot_vars, write_files
+
+    def packed(ds):
+        nat, out = ds._native, []
+        for b in range(nat.num_batches(0)):
+            B, n = nat.batch_shape(0, b)
+            keys = np.zeros(n, dtype=np.uint64)
+            off = np.zeros(B * (nat.n_sparse() + 1), dtype=np.int32)
+            dense = np.zeros(B * nat.dense_dim(), dtype=np.float32)
+            nat.pack_batch(0, b, keys.ctypes.data, off.ctypes.data, dense.ctypes.data, False)
+            out.append((keys, off, dense))
+        return out
+
+    def make(mode):
+        ds = DatasetFactory().create_dataset("InMemoryDataset")
+        ds.set_use_var(slot_vars(5, 3))
+        ds.set_batch_size(16)
+        ds.set_thread(1)
+        ds.set_merge_thread_num(1)
+        ds.set_compact_batches(mode)
+        ds.set_filelist(write_files(str(tmp_path), n_files=1, lines_per_file=70, n_sparse=5, n_dense=3, key_space=50))
+        ds.load_into_memory()
+        ds.prepare_train(1)
+        return ds
+    a, b = make(2), make(0)
+    for (k1, o1, d1), (k2, o2, d2) in zip(packed(a), packed(b)):
+        assert np.array_equal(k1, k2) and np.array_equal(o1, o2) and np.array_equal(d1, d2)
+    assert len(packed(a)) == 5                       # 70 instances -> 4 x 16 + 6
+    a.slots_shuffle(["slot1", "slot3"])
+    b.slots_shuffle(["slot1", "slot3"])
+    for (k1, o1, d1), (k2, o2, d2) in zip(packed(a), packed(b)):
+        assert np.array_equal(k1, k2) and np.array_equal(o1, o2) and np.array_equal(d1, d2)
