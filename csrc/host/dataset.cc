@@ -178,6 +178,28 @@ static inline bool read_u64(const char*& p, const char* e, uint64_t* v) {
 static inline bool read_float(const char*& p, const char* e, float* v) {
   p = skip_ws(p, e);
   if (p >= e) return false;
+  // fast path: [-+]digits[.digits] with at most 18 significant digits and no exponent (what data
+  // generators emit); anything else (exponents, inf/nan, long mantissas) goes through strtof
+  const char* q = p;
+  bool neg = false;
+  if (*q == '-' || *q == '+') { neg = *q == '-'; ++q; }
+  uint64_t mant = 0;
+  int digits = 0, frac = 0;
+  const char* d0 = q;
+  while (q < e && *q >= '0' && *q <= '9') { mant = mant * 10 + (uint64_t)(*q - '0'); ++q; ++digits; }
+  if (q < e && *q == '.') {
+    ++q;
+    while (q < e && *q >= '0' && *q <= '9') { mant = mant * 10 + (uint64_t)(*q - '0'); ++q; ++digits; ++frac; }
+  }
+  const bool ends = q >= e || *q == ' ' || *q == '\t' || *q == '\n' || *q == '\r';
+  if (digits > 0 && digits <= 18 && frac <= 18 && ends && q > d0) {
+    static const double kPow10[19] = {1e0, 1e1, 1e2, 1e3, 1e4, 1e5, 1e6, 1e7, 1e8, 1e9, 1e10, 1e11, 1e12, 1e13,
+                                      1e14, 1e15, 1e16, 1e17, 1e18};
+    const double x = (double)mant / kPow10[frac];     // exact mantissa, one correctly rounded division
+    *v = (float)(neg ? -x : x);
+    p = q;
+    return true;
+  }
   char* end = nullptr;
   *v = strtof(p, &end);
   if (end == p) return false;
@@ -270,21 +292,24 @@ bool Dataset::parse_line(const char* line, size_t len, SlotRecord* rec) const {
         continue;
       }
       if (sd.type == 0) {
-        auto& dst = u64s[slot_to_sparse_[s]];
+        // used sparse slots are numbered in file order: append straight into the record
         for (uint64_t i = 0; i < n; ++i) {
           uint64_t v;
           if (!read_u64(p, e, &v)) return false;
-          if (v != 0 || sd.is_dense) dst.push_back(v);  // zero feasigns dropped (data_feed.cc:4099)
+          if (v != 0 || sd.is_dense) rec->u64_vals.push_back(v);  // zero feasigns dropped (data_feed.cc:4099)
         }
+        rec->u64_offs[slot_to_sparse_[s] + 1] = (uint32_t)rec->u64_vals.size();
       } else {
-        auto& dst = f32s[float_idx_[s]];
         for (uint64_t i = 0; i < n; ++i) {
           float v;
           if (!read_float(p, e, &v)) return false;
-          if (sd.is_dense || std::fabs(v) >= 1e-6f) dst.push_back(v);  // (data_feed.cc:4111)
+          if (sd.is_dense || std::fabs(v) >= 1e-6f) rec->f_vals.push_back(v);  // (data_feed.cc:4111)
         }
+        rec->f_offs[float_idx_[s] + 1] = (uint32_t)rec->f_vals.size();
       }
     }
+    if (n_used_u64_ > 0 && rec->u64_vals.empty()) return false;  // no feasign at all (data_feed.cc:4133)
+    return true;
   }
   size_t total_u64 = 0;
   for (int s = 0; s < n_used_u64_; ++s) {

@@ -390,3 +390,29 @@ def test_compact_arena_pack_matches_record_chase(tmp_path):
     b.slots_shuffle(["slot1", "slot3"])
     for (k1, o1, d1), (k2, o2, d2) in zip(packed(a), packed(b)):
         assert np.array_equal(k1, k2) and np.array_equal(o1, o2) and np.array_equal(d1, d2)
+
+
+def test_fast_float_parser_matches_float32(tmp_path):
+    """The hand-rolled decimal reader gives the float32 nearest to the text for generator-style
+    values, and exotic spellings still go through strtof."""
+    import numpy as np
+    import torch
+    from paddlebox_b200.dataset import DatasetFactory, dense_slot, sparse_slot
+    rng = np.random.default_rng(0)
+    vals = [f"{v:.{int(d)}f}" for v, d in zip(rng.normal(0, 100, 300), rng.integers(0, 9, 300))]
+    vals += ["1e-3", "-2.5E+2", "+7", "0.000001", "123456789012345678", "3.", "-0.0", "1e10"]
+    n = len(vals)
+    path = tmp_path / "part-0"
+    path.write_text(f"{n} " + " ".join(vals) + " 1 5\n")
+    ds = DatasetFactory().create_dataset("InMemoryDataset")
+    ds.set_use_var([dense_slot("f", n), sparse_slot("s")])
+    ds.set_batch_size(1)
+    ds.set_thread(1)
+    ds.set_filelist([str(path)])
+    ds.load_into_memory()
+    assert ds.get_memory_data_size() == 1
+    ds.prepare_train(1)
+    (b,) = list(ds.batches(device=torch.device("cpu")))
+    want = np.array([np.float32(float(v)) for v in vals], dtype=np.float32)
+    got = b.dense[0].numpy()
+    assert np.array_equal(got, want), np.flatnonzero(got != want)
