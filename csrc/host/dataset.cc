@@ -31,50 +31,80 @@ bool ThreadPool::set_cpu_affinity(std::thread& t, int core) {
 }
 
 // ---------------------------------------------------------------- KeyAgent
-// Keys are bucketed into thread-local per-shard buffers; a buffer goes to its shard (one lock) only
-// when it holds a few thousand keys, so the per-key cost is a hash and a push_back.  Every thread
-// that added keys must call flush_local() before the shards are read (merge_loop does).
+// Keys are bucketed into thread-local per-shard buffers; a buffer goes to its shard's set (one
+// lock) only when it holds a few thousand keys.  Every thread that added keys must call
+// flush_local() before the shards are read (merge_loop does).
 static thread_local std::vector<std::vector<uint64_t>> tl_agent_local;
+
+void KeySet::grow() {
+  std::vector<uint64_t> old;
+  old.swap(tab);
+  tab.assign(old.empty() ? 1024 : old.size() * 2, 0);
+  const size_t mask = tab.size() - 1;
+  for (uint64_t k : old) {
+    if (!k) continue;
+    size_t p = (size_t)(mix64(k) >> 20) & mask;
+    while (tab[p]) p = (p + 1) & mask;
+    tab[p] = k;
+  }
+}
+
+inline void KeySet::insert(uint64_t k) {
+  if (k == 0) { has_zero = true; return; }
+  if ((cnt + 1) * 2 > tab.size()) grow();
+  const size_t mask = tab.size() - 1;
+  size_t p = (size_t)(mix64(k) >> 20) & mask;       // (the low bits chose the shard)
+  while (tab[p]) {
+    if (tab[p] == k) return;
+    p = (p + 1) & mask;
+  }
+  tab[p] = k;
+  ++cnt;
+}
+
+void KeySet::dump_sorted(std::vector<uint64_t>* out) const {
+  out->clear();
+  out->reserve(cnt + 1);
+  if (has_zero) out->push_back(0);
+  for (uint64_t k : tab) if (k) out->push_back(k);
+  std::sort(out->begin(), out->end());
+}
+
+void KeyAgent::flush_bucket(size_t s, std::vector<uint64_t>& b) {
+  std::lock_guard<std::mutex> g(mu_[s]);
+  KeySet& set = shards_[s];
+  for (uint64_t k : b) set.insert(k);
+  b.clear();
+}
 
 void KeyAgent::add_keys(const uint64_t* keys, size_t n) {
   const size_t S = shards_.size();
   auto& local = tl_agent_local;
   if (local.size() != S) local.assign(S, {});
   for (size_t i = 0; i < n; ++i) {
-    auto& b = local[mix64(keys[i]) % S];
+    const size_t s = (size_t)(mix64(keys[i]) % S);
+    auto& b = local[s];
     b.push_back(keys[i]);
-    if (b.size() >= 4096) {
-      const size_t s = (size_t)(&b - &local[0]);
-      std::lock_guard<std::mutex> g(mu_[s]);
-      shards_[s].insert(shards_[s].end(), b.begin(), b.end());
-      b.clear();
-    }
+    if (b.size() >= 4096) flush_bucket(s, b);
   }
 }
 
 void KeyAgent::flush_local() {
   auto& local = tl_agent_local;
-  for (size_t s = 0; s < local.size() && s < shards_.size(); ++s) {
-    if (local[s].empty()) continue;
-    std::lock_guard<std::mutex> g(mu_[s]);
-    shards_[s].insert(shards_[s].end(), local[s].begin(), local[s].end());
-    local[s].clear();
-  }
+  for (size_t s = 0; s < local.size() && s < shards_.size(); ++s)
+    if (!local[s].empty()) flush_bucket(s, local[s]);
 }
 
 void KeyAgent::finalize(ThreadPool* pool, std::vector<uint64_t>* out) {
+  std::vector<std::vector<uint64_t>> parts(shards_.size());
   pool->parallel_range(shards_.size(), [&](size_t b, size_t e, int) {
-    for (size_t s = b; s < e; ++s) {
-      auto& v = shards_[s];
-      std::sort(v.begin(), v.end());
-      v.erase(std::unique(v.begin(), v.end()), v.end());
-    }
+    for (size_t s = b; s < e; ++s) shards_[s].dump_sorted(&parts[s]);
   });
   size_t total = 0;
-  for (auto& v : shards_) total += v.size();
+  for (auto& v : parts) total += v.size();
   out->clear();
   out->reserve(total);
-  for (auto& v : shards_) out->insert(out->end(), v.begin(), v.end());
+  for (auto& v : parts) out->insert(out->end(), v.begin(), v.end());
 }
 
 // ---------------------------------------------------------------- batch dealing

@@ -63,17 +63,32 @@ class RecordPool {
 };
 
 // Thread-sharded unique-key collector for the feed pass.
+// Open-addressing set of 64-bit keys (0 is kept aside as "empty" marker).
+struct KeySet {
+  std::vector<uint64_t> tab;
+  size_t cnt = 0;
+  bool has_zero = false;
+  void clear() { std::vector<uint64_t>().swap(tab); cnt = 0; has_zero = false; }
+  void grow();
+  inline void insert(uint64_t k);
+  void dump_sorted(std::vector<uint64_t>* out) const;
+};
+
+// Thread-sharded collector of the pass's unique feasigns (role of boxps::PSAgentBase::AddKeys).
+// Duplicates are dropped on arrival (a pass repeats its hot keys many times), so memory is
+// proportional to the unique keys, not to the feasigns read.
 class KeyAgent {
  public:
   explicit KeyAgent(int shards = 64) : shards_(shards), mu_(shards) {}
   void add_keys(const uint64_t* keys, size_t n);
   void add_key(uint64_t k) { add_keys(&k, 1); flush_local(); }
   void flush_local();   // publish this thread's buffered keys (call before finalize)
-  // sort+unique every shard (parallel) and concatenate
+  // every shard's keys sorted (parallel), shards concatenated
   void finalize(ThreadPool* pool, std::vector<uint64_t>* out);
-  void clear() { for (auto& s : shards_) { s.clear(); s.shrink_to_fit(); } }
+  void clear() { for (auto& s : shards_) s.clear(); }
  private:
-  std::vector<std::vector<uint64_t>> shards_;
+  void flush_bucket(size_t s, std::vector<uint64_t>& b);
+  std::vector<KeySet> shards_;
   std::vector<std::mutex> mu_;
 };
 
