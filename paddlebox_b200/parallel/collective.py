@@ -78,11 +78,23 @@ def c_allreduce_xsum(tensors: Sequence[torch.Tensor], scale: float = 1.0, group=
 
 
 def c_mixallgather(tensors: Sequence[torch.Tensor], mode: int = 0, scale: float | None = None, group=None,
-                   backend: str = "auto"):
+                   backend: str = "auto", topo=None):
     """mode 0: allreduce; 1: reduce-scatter then all-gather (same result, the two halves are
-    what a sharded optimizer interleaves with its update); 2: all-gather of every rank's shard."""
+    what a sharded optimizer interleaves with its update); 2: all-gather of every rank's shard.
+
+    ``topo`` (``parallel.topology.NodeTopology``) with several nodes: modes 0 / 1 run the
+    multi-NIC path of the reference (c_mixallgather_op.cc:231-328) — reduce-scatter inside the
+    node, ``SyncDense`` across nodes on each rank's shard, all-gather inside the node."""
     rank, world = _world(group)
     scale = (1.0 / world) if scale is None else scale
+    if topo is not None and topo.multi_node and mode in (0, 1):
+        flat = torch.cat([t.reshape(-1) for t in tensors])
+        topo.hierarchical_allreduce(flat, scale)
+        off = 0
+        for t in tensors:
+            t.copy_(flat[off:off + t.numel()].view_as(t))
+            off += t.numel()
+        return tensors
     if mode == 0 or world == 1:
         return c_allreduce_xsum(tensors, scale, group, backend)
     cuda = all(t.is_cuda for t in tensors)

@@ -35,9 +35,14 @@ from ..flags import FLAGS
 
 class DenseParamStore:
     def __init__(self, module: nn.Module, rank: int = 0, nranks: int = 1, group=None, use_symm: bool | None = None,
-                 with_moments: bool = True):
+                 with_moments: bool = True, topo=None):
         self.module = module
         self.rank, self.nranks, self.group = rank, nranks, group
+        # more than one node (parallel/topology.py): the symmetric buffer spans this node's GPUs only and
+        # the collectives get an inter-node leg on each rank's shard
+        self.topo = topo if (topo is not None and topo.multi_node) else None
+        self.lrank, self.lsize, self.lgroup = (topo.local_rank, topo.local_size, topo.intra_group) \
+            if self.topo else (rank, nranks, group)
         params = [p for p in module.parameters() if p.requires_grad]
         self.params = params
         self.device = params[0].device if params else torch.device("cpu")
@@ -48,13 +53,13 @@ class DenseParamStore:
             self.offsets.append(off)
             off += (p.numel() + 3) // 4 * 4
         self.numel = max(off, 4)
-        self.use_symm = (self.cuda and nranks > 1 and not FLAGS.dense_use_nccl) if use_symm is None else use_symm
+        self.use_symm = (self.cuda and self.lsize > 1 and not FLAGS.dense_use_nccl) if use_symm is None else use_symm
         self.flat = torch.zeros(self.numel, dtype=torch.float32, device=self.device)
         self.symm = None
         if self.use_symm:
             from .symm import SymmetricBuffer
             # [grads | params] : the params half is only used by sharding / k-step collectives
-            self.symm = SymmetricBuffer(2 * self.numel, rank, nranks, group=group, device=self.device)
+            self.symm = SymmetricBuffer(2 * self.numel, self.lrank, self.lsize, group=self.lgroup, device=self.device)
             self.gflat = self.symm.tensor[:self.numel]
             self.pscratch = self.symm.tensor[self.numel:]
         else:
@@ -75,7 +80,9 @@ class DenseParamStore:
         if self.nranks == 1:
             return
         scale = 1.0 / self.nranks if scale is None else scale
-        if self.use_symm:
+        if self.topo:
+            self.topo.hierarchical_allreduce(self.gflat, scale, self.symm, 0)
+        elif self.use_symm:
             self.symm.allreduce(0, self.numel, scale, stream=stream)
         else:
             import torch.distributed as dist
@@ -88,7 +95,14 @@ class DenseParamStore:
             return
         bufs = [self.flat] + ([self.m, self.v] if with_moments and self.m is not None else [])
         for b in bufs:
-            if self.use_symm:
+            if self.topo:
+                if self.use_symm:
+                    self.pscratch.copy_(b)
+                    self.topo.hierarchical_allreduce(self.pscratch, 1.0 / self.nranks, self.symm, self.numel)
+                    b.copy_(self.pscratch)
+                else:
+                    self.topo.hierarchical_allreduce(b, 1.0 / self.nranks)
+            elif self.use_symm:
                 self.pscratch.copy_(b)
                 self.symm.allreduce(self.numel, self.numel, 1.0 / self.nranks)
                 b.copy_(self.pscratch)
@@ -98,14 +112,25 @@ class DenseParamStore:
                 b.mul_(1.0 / self.nranks)
 
     def shard_range(self):
-        chunk = ((self.numel + self.nranks - 1) // self.nranks + 3) // 4 * 4
-        b = min(self.numel, self.rank * chunk)
+        """Slice this rank's optimizer owns in sharding mode: 1/nranks of the buffer on one node; with
+        several nodes 1/gpus_per_node (every node holds a full replica of the sharded state)."""
+        chunk = ((self.numel + self.lsize - 1) // self.lsize + 3) // 4 * 4
+        b = min(self.numel, self.lrank * chunk)
         return b, min(self.numel, b + chunk)
 
     def reduce_scatter_grads(self) -> None:
         if self.nranks == 1:
             return
-        if self.use_symm:
+        if self.topo:
+            import torch.distributed as dist
+            b, e = self.shard_range()
+            if self.use_symm:
+                self.symm.collective("reduce_scatter", 0, self.numel, 1.0 / self.nranks)
+            else:
+                dist.all_reduce(self.gflat, group=self.lgroup)
+                self.gflat.mul_(1.0 / self.nranks)
+            self.topo.sync_dense(self.gflat[b:e])            # inter-node leg on the owned shard only
+        elif self.use_symm:
             self.symm.collective("reduce_scatter", 0, self.numel, 1.0 / self.nranks)
         else:
             import torch.distributed as dist
@@ -125,7 +150,7 @@ class DenseParamStore:
             b, e = self.shard_range()
             mask = torch.zeros_like(self.flat)
             mask[b:e] = self.flat[b:e]
-            dist.all_reduce(mask, group=self.group)
+            dist.all_reduce(mask, group=self.lgroup)
             self.flat.copy_(mask)
 
     def broadcast_params(self, root: int = 0) -> None:
@@ -211,7 +236,8 @@ class DenseSync:
         every dense gradient of the step is final; see csrc/cuda/sparse_a2a.cu).  Only for the
         plain allreduce mode over symmetric memory with the same ranks as the sparse group."""
         s = self.store
-        if (self.mode != "allreduce" or not s.use_symm or engine is None or not FLAGS.pbx_fold_dense_allreduce
+        if (self.mode != "allreduce" or not s.use_symm or s.topo is not None or engine is None
+                or not FLAGS.pbx_fold_dense_allreduce
                 or getattr(engine, "nranks", 1) != s.nranks):
             return False
         self._fold_desc = (s.symm, 0, s.numel, 1.0 / s.nranks)

@@ -43,7 +43,10 @@ class TrainerConfig:
 
 class CTRTrainer:
     def __init__(self, model: torch.nn.Module, box: BoxWrapper | None = None, config: TrainerConfig | None = None,
-                 rank: int | None = None, world_size: int | None = None, group=None):
+                 rank: int | None = None, world_size: int | None = None, group=None, topo=None):
+        """``topo``: a ``parallel.topology.NodeTopology`` when the job spans several nodes — the dense
+        sync then runs reduce-scatter inside the node, the inter-node leg on each rank's shard and
+        all-gather inside the node (boxps_worker.cc:1220-1233)."""
         self.model = model
         self.box = box or BoxWrapper.get_instance()
         self.cfg = config or TrainerConfig()
@@ -52,7 +55,7 @@ class CTRTrainer:
         mode = "async" if self.cfg.async_mode else self.cfg.sync_dense_mode
         if FLAGS.padbox_enable_sharding_stage:
             mode = "sharding"
-        self.store = DenseParamStore(model, self.rank, self.world, group)
+        self.store = DenseParamStore(model, self.rank, self.world, group, topo=topo)
         self.opt = DenseOptimizer(self.store, lr=self.cfg.dense_lr, kind=self.cfg.dense_optimizer)
         self.sync = DenseSync(self.store, self.opt, mode, self.cfg.sync_weight_step)
         if self.world > 1 and not self.cfg.is_test:

@@ -265,3 +265,50 @@ def cpu_collective_ops(rank, world):
     ok = ok and torch.equal(w, torch.full((3,), 1.0))
     Cc.barrier()
     return bool(ok)
+
+
+def cpu_multi_node_dense(rank, world):
+    """4 ranks as 2 nodes x 2 devices: the three-leg dense sync gives what a flat allreduce gives."""
+    from paddlebox_b200.parallel.dense import DenseOptimizer, DenseParamStore, DenseSync
+    from paddlebox_b200.parallel.topology import NodeTopology
+    topo = NodeTopology(gpus_per_node=2)
+    assert (topo.nnodes, topo.local_size) == (2, 2) and topo.rank == topo.node_rank * 2 + topo.local_rank
+    # raw three-leg allreduce on an odd-sized buffer (the last shard is short)
+    g = torch.Generator().manual_seed(100 + rank)
+    x = torch.randn(37, generator=g)
+    ref = x.clone()
+    dist.all_reduce(ref)
+    topo.hierarchical_allreduce(x, 0.25)
+    assert torch.allclose(x, ref * 0.25, atol=1e-6), (x - ref * 0.25).abs().max()
+    # SyncDense: sum and all-gather across the nodes for one local rank
+    s = torch.full((3,), float(rank))
+    out = topo.sync_dense(s.clone())
+    assert torch.equal(out, torch.full((3,), float(topo.local_rank * 2 + 2)))       # r + (r + 2)
+    ag = topo.sync_dense(s, allgather=True)
+    assert torch.equal(ag, torch.tensor([float(topo.local_rank)] * 3 + [float(topo.local_rank + 2)] * 3))
+    from paddlebox_b200.parallel.collective import c_mixallgather
+    ts = [torch.full((5,), float(rank + 1)), torch.full((2, 3), float(rank))]
+    c_mixallgather(ts, mode=1, topo=topo)
+    assert torch.allclose(ts[0], torch.full((5,), 2.5)) and torch.allclose(ts[1], torch.full((2, 3), 1.5))
+    # the trainer-level modes keep all four replicas identical and equal to the single-node result
+    res = {}
+    for mode in ("allreduce", "kstep", "sharding"):
+        finals = []
+        for use_topo in (True, False):
+            torch.manual_seed(0)
+            model = torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.ReLU(), torch.nn.Linear(5, 1))
+            store = DenseParamStore(model, rank, world, topo=topo if use_topo else None)
+            opt = DenseOptimizer(store, lr=0.05, kind="adam")
+            sync = DenseSync(store, opt, mode, sync_weight_step=2)
+            gen = torch.Generator().manual_seed(7 + rank)
+            for _ in range(4):
+                model(torch.randn(8, 6, generator=gen)).pow(2).mean().backward()
+                sync.after_backward()
+            sync.finalize()
+            gathered = [torch.zeros_like(store.flat) for _ in range(world)]
+            dist.all_gather(gathered, store.flat)
+            assert all(torch.allclose(gathered[0], t, atol=1e-6) for t in gathered), mode
+            finals.append(store.flat.clone())
+        assert torch.allclose(finals[0], finals[1], atol=1e-5), (mode, (finals[0] - finals[1]).abs().max())
+        res[mode] = float(finals[0].sum())
+    return res

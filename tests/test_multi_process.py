@@ -60,6 +60,11 @@ def test_collective_ops_two_ranks_gloo():
     assert all(_spawn(W.cpu_collective_ops, 2, "gloo"))
 
 
+def test_multi_node_dense_sync_four_ranks_gloo():
+    outs = _spawn(W.cpu_multi_node_dense, 4, "gloo")
+    assert outs[0] == outs[3] and set(outs[0]) == {"allreduce", "kstep", "sharding"}
+
+
 def _ngpu():
     return torch.cuda.device_count() if torch.cuda.is_available() else 0
 
