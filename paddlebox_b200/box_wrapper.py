@@ -105,7 +105,8 @@ class BoxWrapper:
         self.config = N.SparseOptConfig()
         self.host_table: HostTable | None = None
         self.table = None          # SparseTable (HBM)
-        self.engine = None         # SparseEngine
+        self.engine = None         # SparseEngine (one node, peer memory)
+        self.router = None         # DistSparseRouter (several nodes / CPU worlds)
         self._phase = 1            # 1 = join, 0 = update (FlipPhase, box_wrapper.h:770-773)
         self._metrics: dict = {}
         self._pass_keys: np.ndarray | None = None
@@ -142,6 +143,7 @@ class BoxWrapper:
         self.lr_map = dict(lr_map or {})
         self.max_keys_per_batch = int(max_keys_per_batch)
         self.host_table = HostTable(self.embedx_dim, self.optimizer, self.config, seed=self.rank)
+        dist_route = self.world_size > 1 and (not self.use_cuda or FLAGS.pbx_sparse_dist)
         if self.use_cuda:
             from .ops.sparse_table import SparseTable
             from .parallel.sparse_engine import SparseEngine
@@ -149,10 +151,16 @@ class BoxWrapper:
             self.table = SparseTable(cap, self.embedx_dim, self.optimizer, self.config, seed=self.rank,
                                      device=self.device.index)
             cap_pair = 0
-            if self.world_size > 1:
+            if self.world_size > 1 and not dist_route:
                 cap_pair = int(FLAGS.pbx_sparse_cap_factor * self.max_keys_per_batch / self.world_size) + 1024
-            self.engine = SparseEngine(self.table, self.max_keys_per_batch, self.rank, self.world_size,
-                                       cap=cap_pair, group=self.group)
+            # (with the all-to-all router the engine serves this rank's shard only: status / dump)
+            self.engine = SparseEngine(self.table, self.max_keys_per_batch, 0 if dist_route else self.rank,
+                                       1 if dist_route else self.world_size, cap=cap_pair, group=self.group)
+        if dist_route:
+            from .parallel.sparse_dist import DistSparseRouter
+            self.router = DistSparseRouter(self.rank, self.world_size, self.hidden, self.group,
+                                           host_table=None if self.use_cuda else self.host_table,
+                                           device_table=self.table if self.use_cuda else None)
         if model_path:
             self.load_model(model_path)
         self._initialized = True
@@ -227,6 +235,9 @@ class BoxWrapper:
     def pull_sparse(self, keys: torch.Tensor, n_dev: torch.Tensor | None = None) -> tuple:
         """Returns (values [U or N, >= hidden], restore int32 [N]); occurrence i's record is
         ``values[restore[i], :hidden]``."""
+        if self.router is not None:
+            n = keys.numel() if n_dev is None else int(n_dev.reshape(-1)[0])
+            return self.router.pull(keys[:n])
         if self.use_cuda:
             restore = self.engine.pull(keys, n_dev=n_dev)
             return self.engine.values, restore
@@ -240,10 +251,14 @@ class BoxWrapper:
         """Per-occurrence gradients [N, hidden] (show, clk counts in the first two columns)."""
         if self._test_mode:
             return
+        from .ops import reference as R
+        if self.router is not None:
+            n_unique = self.router._last[0].numel()
+            self.router.push(R.merge_push(restore, n_unique, grads, key2slot, 2, -float(batch_size)))
+            return
         if self.use_cuda:
             self.engine.push_keys(restore, grads.contiguous(), key2slot, 2, -float(batch_size))
             return
-        from .ops import reference as R
         uk = self._cpu_unique
         merged = R.merge_push(restore, uk.numel(), grads, key2slot, 2, -float(batch_size))
         self.host_table.push(uk.numpy(), merged)
@@ -389,6 +404,7 @@ class BoxWrapper:
 
     def finalize(self) -> None:
         self.engine = None
+        self.router = None
         self.table = None
         self.host_table = None
         self._metrics.clear()

@@ -92,6 +92,7 @@ _d("pbx_use_cuda_graph", True, "capture the training step in a CUDA graph when s
 _d("pbx_pack_threads", 4, "background threads packing mini-batches into staging buffers (per loader)")
 _d("pbx_overlap_wgrad", False, "weight-gradient GEMMs on a side stream, concurrently with the dgrad chain (measured: no gain over the grouped launch)")
 _d("pbx_fold_dense_allreduce", True, "data-parallel dense-gradient allreduce rides on the sparse push kernel's barriers")
+_d("pbx_sparse_dist", False, "GPU worlds: route pull/push through torch.distributed all-to-all (multi-node) instead of the one-node peer-memory engine; CPU worlds with > 1 rank always route this way")
 _d("pbx_sparse_cap_factor", 2.0, "mailbox capacity = factor * max_keys / nranks")
 
 

@@ -173,7 +173,7 @@ class _SparseEmbeddingPool(torch.autograd.Function):
         nothing = (None, None, None, None, None, None)    # the anchor only keeps the node alive
         if box._test_mode:
             return nothing
-        fused_ok = (dout.is_cuda and attrs.cvm_offset == 2 and attrs.embedx_concate_size == 1
+        fused_ok = (dout.is_cuda and box.router is None and attrs.cvm_offset == 2 and attrs.embedx_concate_size == 1
                     and attrs.variant == 0)
         if fused_ok:
             Eo = attrs.out_width(box.hidden)

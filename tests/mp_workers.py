@@ -312,3 +312,76 @@ def cpu_multi_node_dense(rank, world):
         assert torch.allclose(finals[0], finals[1], atol=1e-5), (mode, (finals[0] - finals[1]).abs().max())
         res[mode] = float(finals[0].sum())
     return res
+
+
+def cpu_sharded_sparse_router(rank, world):
+    """CPU world: the table is sharded over the ranks' host tables, pull / push travel over gloo
+    all-to-all, several ranks pushing one key are merged on its owner, a DeepFM trains on top."""
+    from paddlebox_b200.box_wrapper import BoxWrapper, owner_of
+    from paddlebox_b200.models.ctr import DeepFM
+    from paddlebox_b200.ops.pull_box_sparse import SlotBatch
+    from paddlebox_b200.parallel.sparse_dist import owner_of_t
+    from paddlebox_b200.trainer import CTRTrainer, TrainerConfig
+    box = BoxWrapper.set_instance(embedx_dim=8, device=torch.device("cpu"), rank=rank, world_size=world)
+    box.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0, "mf_initial_range": 0.0})
+    assert box.router is not None
+    gen = torch.Generator().manual_seed(100 + rank)
+    B, S, H = 32, 4, 11
+    lens = torch.randint(0, 5, (S * B,), generator=gen)
+    lod = torch.zeros(S * B + 1, dtype=torch.int32)
+    lod[1:] = torch.cumsum(lens, 0)
+    keys = torch.randint(1, 800, (int(lod[-1]),), generator=gen, dtype=torch.int64)
+    assert np.array_equal(owner_of_t(keys, world).numpy(), owner_of(keys.numpy().view(np.uint64), world))
+    box.begin_feed_pass("20240101")
+    box.feed_pass(keys)
+    box.end_feed_pass()
+    owned = box._pass_keys
+    assert np.all(owner_of(owned, world) == rank)
+    rows = box.host_table.fetch_rows(owned, create=True)
+    rows[:, 0] = 50
+    rows[:, 2] = (owned % 97).astype(np.float32)
+    box.host_table.store_rows(owned, rows, mark_dirty=False)
+    box.begin_pass()
+    n_before = box.host_table.size()
+    vals, restore = box.pull_sparse(keys)
+    got = vals[restore.long()]
+    assert torch.equal(got[:, 2], (keys % 97).float()) and torch.all(got[:, 0] == 50)
+    assert box.host_table.size() == n_before, "a pull created rows on a rank that does not own them"
+    grads = torch.zeros(keys.numel(), H)
+    grads[:, 0] = 1.0                                        # one show per occurrence
+    batch = SlotBatch(keys, lod, B, S)
+    box.push_sparse_grad(keys, restore, grads, batch.key2slot(), B)
+    dist.barrier()
+    all_keys = [None] * world
+    dist.all_gather_object(all_keys, keys.numpy())
+    cnt = {}
+    for ks in all_keys:
+        for k in ks.tolist():
+            cnt[k] = cnt.get(k, 0) + 1
+    rows2 = box.host_table.fetch_rows(owned, create=False)
+    for k, r in zip(owned.tolist(), rows2):
+        if k:
+            assert abs(r[0] - (50 + cnt.get(k, 0))) < 1e-4, (k, r[0], cnt.get(k, 0))
+    # data-parallel DeepFM over the routed table
+    dense = torch.rand(B, 4, generator=gen)
+    keys2 = keys.clone()
+    lens2 = torch.clamp(lens, min=1)
+    lod2 = torch.zeros(S * B + 1, dtype=torch.int32)
+    lod2[1:] = torch.cumsum(lens2, 0)
+    keys2 = torch.randint(1, 300, (int(lod2[-1]),), generator=gen, dtype=torch.int64)
+    dense[:, 0] = (keys2[lod2[:B].long()] % 2).float()
+    box.begin_feed_pass("20240102")
+    box.feed_pass(keys2)
+    box.end_feed_pass()
+    box.begin_pass()
+    torch.manual_seed(rank)
+    model = DeepFM(num_slots=S, embedx_dim=8, dense_dim=3, hidden=(16, 8))
+    tr = CTRTrainer(model, box, TrainerConfig(dense_lr=1e-2))
+    b2 = SlotBatch(keys2, lod2, B, S, dense)
+    losses = [float(tr.train_step(b2).detach()) for _ in range(25)]
+    gathered = [torch.zeros_like(tr.store.flat) for _ in range(world)]
+    dist.all_gather(gathered, tr.store.flat)
+    assert all(torch.equal(gathered[0], t) for t in gathered), "dense replicas diverged"
+    assert np.mean(losses[-5:]) < np.mean(losses[:5]), losses
+    box.end_pass()
+    return (losses[0], losses[-1])

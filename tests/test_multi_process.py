@@ -65,6 +65,12 @@ def test_multi_node_dense_sync_four_ranks_gloo():
     assert outs[0] == outs[3] and set(outs[0]) == {"allreduce", "kstep", "sharding"}
 
 
+@pytest.mark.parametrize("world", [2, 3])
+def test_sharded_sparse_over_all_to_all_gloo(world):
+    outs = _spawn(W.cpu_sharded_sparse_router, world, "gloo")
+    assert all(o[1] < o[0] for o in outs)
+
+
 def _ngpu():
     return torch.cuda.device_count() if torch.cuda.is_available() else 0
 
