@@ -8,6 +8,9 @@
 // ctr_dymf_accessor.cc:68-142, :279-315).  The CPU optimizer math restates
 // heter_ps/optimizer.cuh.h:30-472 and must match csrc/cuda/table.cuh bit-for-bit in
 // structure (same layout, same update order).
+#include <fcntl.h>
+#include <unistd.h>
+
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -41,12 +44,204 @@ class HostTable {
     std::vector<uint8_t> dirty;
   };
 
-  size_t shard_of(uint64_t k) const { return mix64(k ^ 0x5bd1e995u) % shards_.size(); }
+  // ---- SSD tier: cold rows leave host memory for one append-only file per shard ------------------
+  // (role of the closed library's SSD tier behind LoadSSD2Mem / CheckNeedLimitMem,
+  //  fleet/box_wrapper.cc:1316-1324, box_wrapper.h:638; open twin: pscore's SSDSparseTable,
+  //  paddle/fluid/distributed/ps/table/ssd_sparse_table.cc.)  A record is the key followed by the
+  //  full value row; the offset of every live record is indexed in memory (16 B per cold key instead
+  //  of a whole row).  A lookup that misses host memory promotes the row back.
+  struct SsdShard {
+    std::unordered_map<uint64_t, uint64_t> index;   // key -> byte offset of its record
+    int fd = -1;
+    uint64_t end = 0;                               // append position
+    uint64_t dead = 0;                              // records superseded or promoted (garbage)
+    std::string path;
+  };
 
-  size_t size() const {
+  size_t shard_of(uint64_t k) const { return mix64(k ^ 0x5bd1e995u) % shards_.size(); }
+  size_t rec_bytes() const { return 8 + (size_t)L.stride * sizeof(float); }
+
+  size_t mem_rows() const {
     size_t n = 0;
     for (auto& s : shards_) n += s.keys.size();
     return n;
+  }
+  size_t ssd_rows() const {
+    size_t n = 0;
+    for (auto& s : ssd_) n += s.index.size();
+    return n;
+  }
+  size_t size() const { return mem_rows() + ssd_rows(); }
+
+  ~HostTable() { ssd_close(false); }
+
+  void ssd_close(bool unlink_files) {
+    for (auto& s : ssd_) {
+      if (s.fd >= 0) close(s.fd);
+      if (unlink_files && !s.path.empty()) unlink(s.path.c_str());
+    }
+    ssd_.clear();
+  }
+
+  int ssd_open(const std::string& dir) {
+    ssd_close(false);
+    ssd_.resize(shards_.size());
+    for (size_t i = 0; i < ssd_.size(); ++i) {
+      char name[512];
+      snprintf(name, sizeof(name), "%s/ssd-%05d.bin", dir.c_str(), (int)i);
+      ssd_[i].path = name;
+      ssd_[i].fd = open(name, O_RDWR | O_CREAT | O_TRUNC, 0644);
+      PBH_REQUIRE(ssd_[i].fd >= 0, "cannot open SSD shard file %s", name);
+    }
+    return 0;
+  }
+
+  bool ssd_read(const SsdShard& d, uint64_t off, uint64_t* key, float* row) const {
+    std::vector<char> buf(rec_bytes());
+    ssize_t got = pread(d.fd, buf.data(), buf.size(), (off_t)off);
+    if (got != (ssize_t)buf.size()) return false;
+    memcpy(key, buf.data(), 8);
+    memcpy(row, buf.data() + 8, (size_t)L.stride * sizeof(float));
+    return true;
+  }
+
+  // rewrites a shard file without its garbage once more than half of it is dead
+  void ssd_compact(SsdShard& d) {
+    if (d.dead < 1024 || d.dead < d.index.size()) return;
+    std::string tmp = d.path + ".tmp";
+    int nfd = open(tmp.c_str(), O_RDWR | O_CREAT | O_TRUNC, 0644);
+    if (nfd < 0) return;
+    std::vector<char> buf(rec_bytes());
+    std::vector<std::pair<uint64_t, uint64_t>> moved;     // key -> offset in the new file
+    moved.reserve(d.index.size());
+    uint64_t pos = 0;
+    bool ok = true;
+    for (auto& kv : d.index) {
+      ok = pread(d.fd, buf.data(), buf.size(), (off_t)kv.second) == (ssize_t)buf.size() &&
+           pwrite(nfd, buf.data(), buf.size(), (off_t)pos) == (ssize_t)buf.size();
+      if (!ok) break;
+      moved.emplace_back(kv.first, pos);
+      pos += buf.size();
+    }
+    if (!ok) {                         // disk full etc.: the old file and its offsets stay as they are
+      close(nfd);
+      unlink(tmp.c_str());
+      return;
+    }
+    for (auto& kv : moved) d.index[kv.first] = kv.second;
+    close(d.fd);
+    rename(tmp.c_str(), d.path.c_str());
+    d.fd = nfd;
+    d.end = pos;
+    d.dead = 0;
+  }
+
+  // Moves rows out of host memory.  Rows unseen for >= min_unseen_days go first (negative: age is
+  // ignored); if the table still holds more than max_mem_rows (> 0), the longest-unseen, then
+  // lowest-score rows follow until it fits.  Rows touched since the last delta save (dirty) and key 0
+  // stay.  Returns the number spilled.
+  int64_t spill(float min_unseen_days, int64_t max_mem_rows, ThreadPool* pool) {
+    if (ssd_.empty()) return 0;
+    const size_t S = shards_.size();
+    std::vector<int64_t> moved(S, 0);
+    const int64_t quota = max_mem_rows > 0 ? std::max<int64_t>(1, max_mem_rows / (int64_t)S) : -1;
+    auto work = [&](size_t si) {
+      Shard& s = shards_[si];
+      SsdShard& d = ssd_[si];
+      const size_t n = s.keys.size();
+      std::vector<uint8_t> go(n, 0);
+      size_t stay = 0;
+      for (size_t i = 0; i < n; ++i) {
+        const float* row = s.rows.data() + i * L.stride;
+        go[i] = s.keys[i] != 0 && !s.dirty[i] && min_unseen_days >= 0.f && row[L.off_tail + 2] >= min_unseen_days;
+        stay += !go[i];
+      }
+      if (quota >= 0 && (int64_t)stay > quota) {
+        std::vector<uint32_t> cand;
+        for (size_t i = 0; i < n; ++i)
+          if (!go[i] && s.keys[i] != 0 && !s.dirty[i]) cand.push_back((uint32_t)i);
+        size_t extra = std::min(cand.size(), stay - (size_t)quota);
+        auto colder = [&](uint32_t a, uint32_t b) {
+          const float* ra = s.rows.data() + (size_t)a * L.stride;
+          const float* rb = s.rows.data() + (size_t)b * L.stride;
+          if (ra[L.off_tail + 2] != rb[L.off_tail + 2]) return ra[L.off_tail + 2] > rb[L.off_tail + 2];
+          return ra[L.off_tail + 0] < rb[L.off_tail + 0];
+        };
+        if (extra < cand.size()) std::nth_element(cand.begin(), cand.begin() + extra, cand.end(), colder);
+        for (size_t j = 0; j < extra; ++j) go[cand[j]] = 1;
+      }
+      std::vector<char> out;
+      Shard ns;
+      for (size_t i = 0; i < n; ++i) {
+        const float* row = s.rows.data() + i * L.stride;
+        if (go[i]) {
+          if (d.index.count(s.keys[i])) ++d.dead;
+          d.index[s.keys[i]] = d.end + out.size();
+          size_t at = out.size();
+          out.resize(at + rec_bytes());
+          memcpy(out.data() + at, &s.keys[i], 8);
+          memcpy(out.data() + at + 8, row, (size_t)L.stride * sizeof(float));
+          ++moved[si];
+        } else {
+          ns.index.emplace(s.keys[i], (uint32_t)ns.keys.size());
+          ns.keys.push_back(s.keys[i]);
+          ns.dirty.push_back(s.dirty[i]);
+          ns.rows.insert(ns.rows.end(), row, row + L.stride);
+        }
+      }
+      if (out.empty()) return;
+      if (pwrite(d.fd, out.data(), out.size(), (off_t)d.end) != (ssize_t)out.size()) {
+        // the write failed: forget the new offsets, keep every row in memory
+        uint64_t key;
+        for (size_t at = 0; at < out.size(); at += rec_bytes()) { memcpy(&key, out.data() + at, 8); d.index.erase(key); }
+        moved[si] = 0;
+        return;
+      }
+      d.end += out.size();
+      s = std::move(ns);
+      ssd_compact(d);
+    };
+    if (pool) pool->parallel_range(S, [&](size_t b, size_t e, int) { for (size_t i = b; i < e; ++i) work(i); });
+    else for (size_t i = 0; i < S; ++i) work(i);
+    int64_t total = 0;
+    for (auto m : moved) total += m;
+    return total;
+  }
+
+  // row of `key` comes back from its shard file into host memory (nullptr when it is not there)
+  float* promote(Shard& s, SsdShard& d, uint64_t key) {
+    auto it = d.index.find(key);
+    if (it == d.index.end()) return nullptr;
+    std::vector<float> row(L.stride);
+    uint64_t k2 = 0;
+    if (!ssd_read(d, it->second, &k2, row.data()) || k2 != key) return nullptr;
+    d.index.erase(it);
+    ++d.dead;
+    uint32_t idx = (uint32_t)s.keys.size();
+    s.index.emplace(key, idx);
+    s.keys.push_back(key);
+    s.dirty.push_back(0);
+    s.rows.insert(s.rows.end(), row.begin(), row.end());
+    return s.rows.data() + (size_t)idx * L.stride;
+  }
+
+  // LoadSSD2Mem: every cold row returns to host memory (before a day-end shrink / base save)
+  int64_t load_ssd2mem(ThreadPool* pool) {
+    if (ssd_.empty()) return 0;
+    const size_t S = shards_.size();
+    std::vector<int64_t> cnt(S, 0);
+    auto work = [&](size_t si) {
+      std::vector<uint64_t> ks;
+      for (auto& kv : ssd_[si].index) ks.push_back(kv.first);
+      for (uint64_t k : ks) cnt[si] += promote(shards_[si], ssd_[si], k) != nullptr;
+      SsdShard& d = ssd_[si];
+      if (d.index.empty() && d.fd >= 0 && ftruncate(d.fd, 0) == 0) { d.end = 0; d.dead = 0; }
+    };
+    if (pool) pool->parallel_range(S, [&](size_t b, size_t e, int) { for (size_t i = b; i < e; ++i) work(i); });
+    else for (size_t i = 0; i < S; ++i) work(i);
+    int64_t total = 0;
+    for (auto c : cnt) total += c;
+    return total;
   }
 
   void init_row(float* row, uint64_t key) const {
@@ -63,6 +258,9 @@ class HostTable {
     auto it = s.index.find(key);
     if (fresh) *fresh = false;
     if (it != s.index.end()) return s.rows.data() + (size_t)it->second * L.stride;
+    if (!ssd_.empty()) {
+      if (float* cold = promote(s, ssd_[shard_of(key)], key)) return cold;
+    }
     if (!create) return nullptr;
     uint32_t idx = (uint32_t)s.keys.size();
     s.index.emplace(key, idx);
@@ -188,6 +386,7 @@ class HostTable {
   // decay + evict (CtrDymfAccessor::Shrink); returns survivors
   int64_t shrink(float decay, float delete_threshold, float delete_after_unseen_days) {
     int64_t kept = 0;
+    load_ssd2mem(nullptr);        // decay and ageing apply to every row, cold ones included
     for (auto& s : shards_) {
       Shard ns;
       for (size_t i = 0; i < s.keys.size(); ++i) {
@@ -223,15 +422,22 @@ class HostTable {
       snprintf(name, sizeof(name), "%s/part-%03d-%05d", dir.c_str(), part_shard_base, (int)si);
       FILE* fp = fopen(name, "w");
       PBH_REQUIRE(fp != nullptr, "cannot open %s for writing", name);
-      for (size_t i = 0; i < s.keys.size(); ++i) {
-        const float* row = s.rows.data() + i * L.stride;
+      // rows in host memory first, then the shard's cold rows straight from its SSD file (never dirty)
+      std::vector<std::pair<uint64_t, uint64_t>> cold;
+      if (!ssd_.empty() && mode != 1) cold.assign(ssd_[si].index.begin(), ssd_[si].index.end());
+      std::vector<float> cold_row(L.stride);
+      for (size_t i = 0; i < s.keys.size() + cold.size(); ++i) {
+        const bool in_mem = i < s.keys.size();
+        uint64_t key = in_mem ? s.keys[i] : cold[i - s.keys.size()].first;
+        if (!in_mem && !ssd_read(ssd_[si], cold[i - s.keys.size()].second, &key, cold_row.data())) continue;
+        const float* row = in_mem ? s.rows.data() + i * L.stride : cold_row.data();
         float score = cfg.nonclk_coeff * (row[0] - row[1]) + cfg.clk_coeff * row[1];
         if (mode == 1 && !(s.dirty[i] && score >= delta_threshold)) continue;
         if (mode == 2 && score < base_threshold) continue;
         const bool serving = (mode == 1 || mode == 2);
         const int D = L.embedx_dim;
         const bool has_mf = row[L.off_mf] != 0.f;
-        fprintf(fp, "%llu %g %g %g %g %.9g", (unsigned long long)s.keys[i], row[L.off_tail + 2], row[L.off_tail + 0],
+        fprintf(fp, "%llu %g %g %g %g %.9g", (unsigned long long)key, row[L.off_tail + 2], row[L.off_tail + 0],
                 row[0], row[1], row[2]);
         if (!serving) for (int j = 0; j < L.embed_state; ++j) fprintf(fp, " %.9g", row[L.off_es + j]);
         fprintf(fp, " %d %d", (int)row[L.off_tail + 1], has_mf ? D : 0);
@@ -241,7 +447,7 @@ class HostTable {
         }
         fputc('\n', fp);
         ++total;
-        if (clear_dirty && mode == 1) s.dirty[i] = 0;
+        if (clear_dirty && mode == 1 && in_mem) s.dirty[i] = 0;
       }
       fclose(fp);
     }
@@ -299,9 +505,17 @@ class HostTable {
   void all_keys(std::vector<uint64_t>* out) const {
     out->clear();
     for (auto& s : shards_) out->insert(out->end(), s.keys.begin(), s.keys.end());
+    for (auto& d : ssd_)
+      for (auto& kv : d.index) out->push_back(kv.first);
   }
 
-  void clear() { for (auto& s : shards_) s = Shard(); }
+  void clear() {
+    for (auto& s : shards_) s = Shard();
+    for (auto& d : ssd_) {
+      d.index.clear();
+      if (d.fd >= 0 && ftruncate(d.fd, 0) == 0) { d.end = 0; d.dead = 0; }
+    }
+  }
 
  private:
   template <typename F>
@@ -323,6 +537,7 @@ class HostTable {
     (void)S;
   }
   std::vector<Shard> shards_;
+  std::vector<SsdShard> ssd_;
   std::vector<std::mutex> mu_;
 };
 
@@ -372,6 +587,14 @@ int pbh_table_save(void* h, const char* dir, int mode, int part_shard_base, floa
 int pbh_table_load_file(void* h, const char* path, int serving, int64_t* n_loaded) {
   return ((HostTable*)h)->load_file(path, serving != 0, n_loaded);
 }
+int pbh_table_ssd_open(void* h, const char* dir) { return ((HostTable*)h)->ssd_open(dir); }
+int pbh_table_ssd_close(void* h, int unlink_files) { ((HostTable*)h)->ssd_close(unlink_files != 0); return 0; }
+int64_t pbh_table_spill(void* h, float min_unseen_days, int64_t max_mem_rows) {
+  return ((HostTable*)h)->spill(min_unseen_days, max_mem_rows, table_pool());
+}
+int64_t pbh_table_load_ssd2mem(void* h) { return ((HostTable*)h)->load_ssd2mem(table_pool()); }
+int64_t pbh_table_mem_rows(void* h) { return (int64_t)((HostTable*)h)->mem_rows(); }
+int64_t pbh_table_ssd_rows(void* h) { return (int64_t)((HostTable*)h)->ssd_rows(); }
 int64_t pbh_table_keys(void* h, uint64_t* out, int64_t max_n) {
   std::vector<uint64_t> ks;
   ((HostTable*)h)->all_keys(&ks);

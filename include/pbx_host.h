@@ -83,6 +83,16 @@ int pbh_table_save(void* t, const char* dir, int mode, int part_shard_base, floa
                    float delta_threshold, int clear_dirty, int64_t* n_saved);
 int pbh_table_load_file(void* t, const char* path, int serving, int64_t* n_loaded);
 int64_t pbh_table_keys(void* t, uint64_t* out, int64_t max_n);
+/* SSD tier (closed-library LoadSSD2Mem / CheckNeedLimitMem, fleet/box_wrapper.cc:1316-1324): cold rows
+ * move to one append-only file per shard under `dir`; a lookup that misses host memory promotes the
+ * row back.  spill: rows unseen for >= min_unseen_days (negative: ignore age), then — if
+ * max_mem_rows > 0 — the longest-unseen rows until the memory tier fits; dirty rows stay. */
+int pbh_table_ssd_open(void* t, const char* dir);
+int pbh_table_ssd_close(void* t, int unlink_files);
+int64_t pbh_table_spill(void* t, float min_unseen_days, int64_t max_mem_rows);
+int64_t pbh_table_load_ssd2mem(void* t);
+int64_t pbh_table_mem_rows(void* t);
+int64_t pbh_table_ssd_rows(void* t);
 
 /* ---- AUC calculators (csrc/host/metrics.cc); reference fleet/metrics.cc:38-587 ---- */
 int pbh_auc_create(void** out, int table_size);

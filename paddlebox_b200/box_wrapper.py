@@ -117,6 +117,9 @@ class BoxWrapper:
         self.timers = StageTimers()
         self.slot_vector: list = []
         self.lr_map: dict = {}
+        self.host_mem_rows_limit = 0
+        self.ssd_unseen_days = -1.0
+        self._ssd = False
         self._initialized = False
 
     # ---- initialisation ----------------------------------------------------------------
@@ -134,6 +137,9 @@ class BoxWrapper:
         elif conf_file:
             with open(conf_file) as f:
                 conf = json.load(f)
+        ssd_dir = conf.pop("ssd_dir", "")
+        self.host_mem_rows_limit = int(conf.pop("host_mem_rows_limit", 0))
+        self.ssd_unseen_days = float(conf.pop("ssd_unseen_days", -1.0))
         table_capacity = conf.pop("table_capacity", table_capacity)
         max_keys_per_batch = conf.pop("max_keys_per_batch", max_keys_per_batch)
         self.optimizer = conf.pop("optimizer", self.optimizer)
@@ -143,6 +149,9 @@ class BoxWrapper:
         self.lr_map = dict(lr_map or {})
         self.max_keys_per_batch = int(max_keys_per_batch)
         self.host_table = HostTable(self.embedx_dim, self.optimizer, self.config, seed=self.rank)
+        if ssd_dir:
+            self.host_table.ssd_open(os.path.join(ssd_dir, f"rank{self.rank:03d}"))
+            self._ssd = True
         dist_route = self.world_size > 1 and (not self.use_cuda or FLAGS.pbx_sparse_dist)
         if self.use_cuda:
             from .ops.sparse_table import SparseTable
@@ -229,6 +238,9 @@ class BoxWrapper:
         self._in_pass = False
         if need_save_delta and delta_path:
             self.save_delta(delta_path)
+        if self._ssd and self.check_need_limit_mem():
+            # host tier over its budget: the coldest rows go to the SSD tier
+            self.host_table.spill(self.ssd_unseen_days, self.host_mem_rows_limit)
         self.timers.add("end_pass", time.time() - t0)
 
     # ---- pull / push (single call; autograd wrappers live in ops/pull_box_sparse.py) ----------
@@ -296,8 +308,13 @@ class BoxWrapper:
     def load_model(self, path: str, serving: bool = False) -> int:
         return self.host_table.load(path, serving=serving)
 
-    def load_ssd2mem(self, date: str = "") -> None:
-        """Host-spill hook; the table is HBM + host-memory resident here."""
+    def load_ssd2mem(self, date: str = "") -> int:
+        """Bring every row of the SSD tier back into host memory (``LoadSSD2Mem(day)``,
+        box_wrapper.cc:1316-1324) — called before the day-end ``shrink_table`` / ``save_base``.
+        Returns the number of rows loaded (0 without an SSD tier: conf ``ssd_dir``)."""
+        if date:
+            self.set_date(date)
+        return self.host_table.load_ssd2mem() if self._ssd else 0
 
     def shrink_table(self, decay: float = 0.98, delete_threshold: float = 0.0,
                      delete_after_unseen_days: float = 30.0) -> int:
@@ -347,6 +364,12 @@ class BoxWrapper:
             self.table.set_test_mode(on)
 
     def check_need_limit_mem(self) -> bool:
+        """True when a memory tier is over its budget: the host tier holds more rows than conf
+        ``host_mem_rows_limit`` (then ``end_pass`` spills to the SSD tier), or the GPU has less
+        than 10 % of its memory free."""
+        if self.host_mem_rows_limit and self.host_table is not None \
+                and self.host_table.mem_rows() > self.host_mem_rows_limit:
+            return True
         if not self.use_cuda:
             return False
         free, total = torch.cuda.mem_get_info(self.device)

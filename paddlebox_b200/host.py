@@ -119,6 +119,33 @@ class HostTable:
             total += n.value
         return total
 
+    # ---- SSD tier ----------------------------------------------------------------------------
+    def ssd_open(self, directory: str) -> None:
+        """Enable the SSD tier: one append-only file per shard under ``directory``."""
+        os.makedirs(directory, exist_ok=True)
+        N.hcheck(N.host().pbh_table_ssd_open(self._h, directory.encode()))
+
+    def ssd_close(self, unlink: bool = False) -> None:
+        N.hcheck(N.host().pbh_table_ssd_close(self._h, int(unlink)))
+
+    def _i64(self, name: str, *args) -> int:
+        fn = getattr(N.host(), name)
+        fn.restype = C.c_int64
+        return fn(self._h, *args)
+
+    def spill(self, min_unseen_days: float = -1.0, max_mem_rows: int = 0) -> int:
+        """Move cold rows to the SSD tier; returns how many went (see include/pbx_host.h)."""
+        return self._i64("pbh_table_spill", C.c_float(min_unseen_days), C.c_int64(max_mem_rows))
+
+    def load_ssd2mem(self) -> int:
+        return self._i64("pbh_table_load_ssd2mem")
+
+    def mem_rows(self) -> int:
+        return self._i64("pbh_table_mem_rows")
+
+    def ssd_rows(self) -> int:
+        return self._i64("pbh_table_ssd_rows")
+
     def keys(self) -> np.ndarray:
         n = N.host().pbh_table_keys(self._h, None, C.c_int64(0))
         out = np.empty(n, dtype=np.uint64)

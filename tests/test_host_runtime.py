@@ -232,6 +232,88 @@ def test_host_table_checkpoint_roundtrip_and_shrink(tmp_path):
     assert kept == 60 and t.size() == 60
 
 
+def test_host_table_ssd_tier(tmp_path):
+    """Cold rows spill to the per-shard SSD files, come back on lookup / push / LoadSSD2Mem, and are
+    part of every full save; dirty rows stay in memory."""
+    cfg = N.SparseOptConfig(mf_create_thresholds=0.0, mf_initial_range=0.01)
+    t = HostTable(4, "adagrad", cfg)
+    t.ssd_open(str(tmp_path / "ssd"))
+    keys = np.arange(1, 5001, dtype=np.uint64)
+    rows = t.fetch_rows(keys)
+    rows[:, 2] = (keys % 97).astype(np.float32)
+    age = t.layout.off_tail + 2
+    rows[:, age] = (keys % 10).astype(np.float32)           # unseen days 0..9
+    t.store_rows(keys, rows, mark_dirty=False)
+    t.store_rows(keys[:50], rows[:50], mark_dirty=True)      # touched in the current delta window
+    ref = t.fetch_rows(keys, create=False).copy()
+    # by age: every clean row unseen for >= 5 days goes
+    n_old = int(((keys % 10) >= 5)[50:].sum())
+    assert t.spill(min_unseen_days=5.0) == n_old
+    assert t.ssd_rows() == n_old and t.mem_rows() == 5000 - n_old and t.size() == 5000
+    # by budget: the memory tier shrinks to about the limit, oldest first; dirty rows stay
+    t.spill(max_mem_rows=1280)
+    assert t.mem_rows() <= 1280 + 64 + 50 and t.size() == 5000
+    assert len(np.unique(t.keys())) == 5000
+    # a full save streams the cold rows too; a delta holds the dirty rows only
+    assert t.save(str(tmp_path / "batch"), mode=0, clear_dirty=False) == 5000
+    assert t.save(str(tmp_path / "delta"), mode=1, clear_dirty=False) == 50
+    t2 = HostTable(4, "adagrad", cfg)
+    assert t2.load(str(tmp_path / "batch")) == 5000
+    assert np.allclose(t2.fetch_rows(keys, create=False), ref, rtol=1e-6, atol=1e-7)
+    # pull promotes exactly what it touches, values intact
+    cold_before = t.ssd_rows()
+    probe = keys[4000:4100]
+    got = t.pull(probe)
+    assert torch.equal(got[:, 2], torch.from_numpy((probe % 97).astype(np.float32)))
+    assert t.size() == 5000 and t.ssd_rows() <= cold_before
+    # a push on a cold key updates the promoted row
+    push = np.zeros((1, t.layout.push_stride), dtype=np.float32)
+    push[0, 1] = 3
+    k = keys[4999:5000]
+    show0 = ref[4999, 0]
+    t.push(k, push)
+    assert t.fetch_rows(k, create=False)[0, 0] == show0 + 3
+    # spill / promote cycles leave garbage behind; the files are compacted and nothing is lost
+    for _ in range(4):
+        t.save(str(tmp_path / "d"), mode=1, clear_dirty=True)
+        t.spill(max_mem_rows=640)
+        t.pull(keys[::3])
+    assert t.size() == 5000
+    # LoadSSD2Mem brings everything back; rows equal the reference except the pushed one
+    n_cold = t.ssd_rows()
+    assert t.load_ssd2mem() == n_cold and t.ssd_rows() == 0 and t.mem_rows() == 5000
+    back = t.fetch_rows(keys, create=False)
+    assert np.allclose(back[:4999], ref[:4999], rtol=1e-6, atol=1e-7)
+    # shrink sees cold rows as well
+    t.spill(max_mem_rows=640)
+    kept = t.shrink(decay=1.0, delete_threshold=-1e9, delete_after_unseen_days=7.5)
+    assert kept == 3500 and t.size() == 3500 and t.ssd_rows() == 0      # ages 0..6 survive one more day
+    t.ssd_close(unlink=True)
+    assert not any(f.endswith(".bin") for f in os.listdir(tmp_path / "ssd"))
+
+
+def test_box_wrapper_spills_at_end_pass(tmp_path):
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    BoxWrapper.reset_instance()
+    box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=0, world_size=1)
+    try:
+        box.initialize_gpu_and_load_model({"ssd_dir": str(tmp_path / "ssd"), "host_mem_rows_limit": 640})
+        for day, lo in (("20240101", 1), ("20240102", 3001)):
+            box.begin_feed_pass(day)
+            box.feed_pass(np.arange(lo, lo + 3000, dtype=np.uint64))
+            box.end_feed_pass()
+            box.begin_pass()
+            box.end_pass()
+            box.save_delta(str(tmp_path / f"delta{day}"))
+        assert box.check_need_limit_mem() is False or box.host_table.mem_rows() <= 3000 + 640
+        assert box.host_table.ssd_rows() > 0 and box.host_table.size() == 6001      # + key 0
+        vals, restore = box.pull_sparse(torch.arange(1, 50, dtype=torch.int64))   # day-1 keys come back
+        assert vals.shape[0] == 49
+        assert box.load_ssd2mem("20240103") > 0 and box.host_table.ssd_rows() == 0
+    finally:
+        BoxWrapper.reset_instance()
+
+
 # ---------------------------------------------------------------- metrics
 def test_auc_matches_exact_and_components():
     rs = np.random.RandomState(0)
