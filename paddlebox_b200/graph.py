@@ -1,0 +1,282 @@
+"""Graph engine: typed edge tables, neighbour sampling, random walks, walk-pair batches.
+
+Reference role: ``GraphGpuWrapper`` / ``GpuPsGraphTable`` (heter_ps/graph_gpu_wrapper.h:34-99,
+graph_gpu_ps_table_inl.cu) and ``GraphDataGenerator`` (data_feed.h:892-975, data_feed.cu:200-1206):
+the graph lives next to the parameter server, walks over it produce (centre, context) node pairs,
+and the node ids are feasigns whose embeddings are pulled / pushed like any other slot.
+
+Here
+
+* ``GraphTable`` is the native host store (csrc/host/graph.cc): edge lists -> CSR per edge type,
+  multi-threaded sampling and (metapath) walks on the host;
+* ``DeviceGraph`` is the same CSR resident in HBM: a B200 holds ~10 G edges in its 180 GB, so the
+  whole graph of one rank stays on the device and sampling / walking is a handful of gather ops per
+  step with no host round trip (the reference pages partitions through ``load_next_partition``);
+* ``GraphDataGenerator`` turns walks into skip-gram batches in the ``SlotBatch`` layout (slot 0 =
+  centre node, slot 1 = context node, one key per bag), so the sparse path is the stock one;
+* ``GraphGpuWrapper`` keeps the reference's method names.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Iterator, Sequence
+
+import numpy as np
+import torch
+
+from . import _native as N
+
+
+def _u64p(a):
+    return a.ctypes.data_as(C.POINTER(C.c_uint64))
+
+
+class GraphTable:
+    """Host graph store; edge type = small integer."""
+
+    def __init__(self):
+        self._h = C.c_void_p()
+        lib = N.host()
+        N.hcheck(lib.pbh_graph_create(C.byref(self._h)))
+        lib.pbh_graph_num_nodes.restype = C.c_int64
+        lib.pbh_graph_num_edges.restype = C.c_int64
+
+    def __del__(self):
+        try:
+            if self._h:
+                N.host().pbh_graph_destroy(self._h)
+                self._h = C.c_void_p()
+        except Exception:
+            pass
+
+    # ---- construction -------------------------------------------------------------------------
+    def add_edges(self, src, dst, etype: int = 0, reverse: bool = False) -> None:
+        s = np.ascontiguousarray(src, dtype=np.uint64)
+        d = np.ascontiguousarray(dst, dtype=np.uint64)
+        assert s.shape == d.shape
+        N.hcheck(N.host().pbh_graph_add_edges(self._h, etype, _u64p(s), _u64p(d), C.c_int64(s.size), int(reverse)))
+
+    def load_edge_file(self, path: str, etype: int = 0, reverse: bool = False) -> int:
+        """Text file ``src<TAB>dst`` per line; ``reverse`` stores dst -> src."""
+        n = C.c_int64()
+        N.hcheck(N.host().pbh_graph_load_edge_file(self._h, etype, path.encode(), int(reverse), C.byref(n)))
+        return n.value
+
+    def build(self, etype: int = 0) -> None:
+        N.hcheck(N.host().pbh_graph_build(self._h, etype))
+
+    def num_nodes(self, etype: int = 0) -> int:
+        return N.host().pbh_graph_num_nodes(self._h, etype)
+
+    def num_edges(self, etype: int = 0) -> int:
+        return N.host().pbh_graph_num_edges(self._h, etype)
+
+    def csr(self, etype: int = 0):
+        """(node_ids uint64 [n] sorted, row_ptr int64 [n+1], col int64 [m] neighbour indices)."""
+        n, m = self.num_nodes(etype), self.num_edges(etype)
+        ids = np.empty(n, np.uint64)
+        rp = np.empty(n + 1, np.int64)
+        col = np.empty(m, np.int64)
+        N.hcheck(N.host().pbh_graph_export_csr(self._h, etype, _u64p(ids), rp.ctypes.data_as(C.POINTER(C.c_int64)),
+                                               col.ctypes.data_as(C.POINTER(C.c_int64))))
+        return ids, rp, col
+
+    def all_ids(self, etype: int = 0) -> np.ndarray:
+        return self.csr(etype)[0]
+
+    # ---- host sampling --------------------------------------------------------------------------
+    def sample_neighbors(self, nodes, k: int, etype: int = 0, seed: int = 0):
+        """(neighbours uint64 [n, k], counts int32 [n]); without replacement, unused entries 0."""
+        q = np.ascontiguousarray(nodes, dtype=np.uint64)
+        out = np.empty((q.size, k), np.uint64)
+        cnt = np.empty(q.size, np.int32)
+        N.hcheck(N.host().pbh_graph_sample_neighbors(self._h, etype, _u64p(q), C.c_int64(q.size), k, C.c_uint64(seed),
+                                                     _u64p(out), cnt.ctypes.data_as(C.POINTER(C.c_int32))))
+        return out, cnt
+
+    def random_walk(self, starts, walk_len: int, metapath: Sequence[int] = (0,), seed: int = 0):
+        """(walks uint64 [n, walk_len], lengths int32 [n]); step s follows edge type
+        ``metapath[s % len]``; a walk ends early at a node without out-edges (rest of the row 0)."""
+        q = np.ascontiguousarray(starts, dtype=np.uint64)
+        mp = (C.c_int * len(metapath))(*metapath)
+        out = np.empty((q.size, walk_len), np.uint64)
+        ln = np.empty(q.size, np.int32)
+        N.hcheck(N.host().pbh_graph_random_walk(self._h, mp, len(metapath), _u64p(q), C.c_int64(q.size), walk_len,
+                                                C.c_uint64(seed), _u64p(out), ln.ctypes.data_as(C.POINTER(C.c_int32))))
+        return out, ln
+
+    def to_device(self, device=None, etypes: Sequence[int] | None = None) -> "DeviceGraph":
+        n_types = N.host().pbh_graph_num_types(self._h)
+        return DeviceGraph({t: self.csr(t) for t in (etypes if etypes is not None else range(n_types))}, device)
+
+
+class DeviceGraph:
+    """CSR of every edge type as tensors on one device; sampling and walking are gathers there.
+    Node ids are int64 on the device (the uint64 bit pattern, as for every key)."""
+
+    def __init__(self, csr_by_type: dict, device=None):
+        self.device = torch.device(device) if device is not None else torch.device(
+            "cuda", torch.cuda.current_device()) if torch.cuda.is_available() else torch.device("cpu")
+        self.types = {}
+        for t, (ids, rp, col) in csr_by_type.items():
+            self.types[t] = (torch.from_numpy(ids.view(np.int64)).to(self.device),
+                             torch.from_numpy(rp).to(self.device), torch.from_numpy(col).to(self.device))
+
+    def index_of(self, nodes: torch.Tensor, etype: int = 0):
+        """(index int64 [n], known bool [n]).  Ids are sorted as uint64; int64 order differs only for
+        ids >= 2^63, which are mapped through an order-preserving flip of the sign bit."""
+        ids = self.types[etype][0]
+        flip = torch.iinfo(torch.int64).min
+        idx = torch.searchsorted(ids ^ flip, nodes ^ flip).clamp_(max=max(ids.numel() - 1, 0))
+        known = ids[idx] == nodes if ids.numel() else torch.zeros_like(nodes, dtype=torch.bool)
+        return idx, known
+
+    def degree(self, nodes: torch.Tensor, etype: int = 0) -> torch.Tensor:
+        _, rp, _ = self.types[etype]
+        idx, known = self.index_of(nodes, etype)
+        return torch.where(known, rp[idx + 1] - rp[idx], torch.zeros_like(idx))
+
+    def sample_neighbors(self, nodes: torch.Tensor, k: int, etype: int = 0, generator=None):
+        """(neighbours int64 [n, k], counts int64 [n]).  Nodes with <= k neighbours return all of them
+        (in id order); larger neighbourhoods are sampled uniformly WITH replacement (one gather per
+        sample instead of a per-node shuffle).  Unused entries are 0."""
+        ids, rp, col = self.types[etype]
+        idx, known = self.index_of(nodes, etype)
+        deg = torch.where(known, rp[idx + 1] - rp[idx], torch.zeros_like(idx))
+        n = nodes.numel()
+        j = torch.arange(k, device=self.device).expand(n, k)
+        r = torch.rand(n, k, device=self.device, generator=generator)
+        pick = torch.where((deg > k)[:, None], (r * deg[:, None]).long(), j)
+        cnt = deg.clamp(max=k)
+        valid = j < cnt[:, None]
+        pos = (rp[idx][:, None] + torch.minimum(pick, (deg - 1).clamp(min=0)[:, None])).clamp_(max=max(col.numel() - 1, 0))
+        nb = ids[col[pos]] if col.numel() else torch.zeros(n, k, dtype=torch.int64, device=self.device)
+        return torch.where(valid, nb, torch.zeros_like(nb)), cnt
+
+    def random_walk(self, starts: torch.Tensor, walk_len: int, metapath: Sequence[int] = (0,), generator=None):
+        """(walks int64 [n, walk_len], lengths int64 [n]); same contract as ``GraphTable.random_walk``."""
+        n = starts.numel()
+        walks = torch.zeros(n, walk_len, dtype=torch.int64, device=self.device)
+        walks[:, 0] = starts
+        alive = torch.ones(n, dtype=torch.bool, device=self.device)
+        length = torch.ones(n, dtype=torch.int64, device=self.device)
+        cur = starts
+        for s in range(1, walk_len):
+            ids, rp, col = self.types[metapath[(s - 1) % len(metapath)]]
+            idx, known = self.index_of(cur, metapath[(s - 1) % len(metapath)])
+            deg = torch.where(known, rp[idx + 1] - rp[idx], torch.zeros_like(idx))
+            alive = alive & (deg > 0)
+            r = torch.rand(n, device=self.device, generator=generator)
+            pos = (rp[idx] + torch.minimum((r * deg).long(), (deg - 1).clamp(min=0))).clamp_(max=max(col.numel() - 1, 0))
+            nxt = ids[col[pos]] if col.numel() else cur
+            cur = torch.where(alive, nxt, cur)
+            walks[:, s] = torch.where(alive, cur, torch.zeros_like(cur))
+            length += alive.long()
+        return walks, length
+
+
+def walk_pairs(walks: torch.Tensor, lengths: torch.Tensor, window: int):
+    """Skip-gram pairs of every walk: (centre, context) for |i - j| <= window, i != j, both inside
+    the walk's valid prefix (GraphDataGenerator's pair kernel, data_feed.cu:260-330)."""
+    n, L = walks.shape
+    i = torch.arange(L, device=walks.device)
+    off = torch.cat([torch.arange(-window, 0, device=walks.device), torch.arange(1, window + 1, device=walks.device)])
+    ci = i[:, None].expand(L, off.numel())
+    cj = ci + off[None, :]
+    ok = (cj >= 0) & (cj < L)
+    ci, cj = ci[ok], cj[ok]                                  # [P] position pairs shared by all walks
+    valid = (ci[None, :] < lengths[:, None]) & (cj[None, :] < lengths[:, None])
+    return walks[:, ci][valid], walks[:, cj][valid]
+
+
+class GraphDataGenerator:
+    """Walks -> skip-gram mini-batches with sampled negatives.
+
+    Every batch holds ``batch_size`` rows: ``1/(1+neg)`` of them positive pairs from the walks,
+    the rest the same centres with a uniformly drawn node as context (label 0).  Rows are shuffled.
+    ``batches()`` yields ``SlotBatch`` objects (2 slots, one key per bag, ``dense[:, 0]`` = label)."""
+
+    def __init__(self, graph: "DeviceGraph | GraphTable", walk_len: int = 8, window: int = 2, batch_size: int = 1024,
+                 neg: int = 2, metapath: Sequence[int] = (0,), walks_per_node: int = 1, seed: int = 0, device=None):
+        self.graph = graph if isinstance(graph, DeviceGraph) else graph.to_device(device)
+        self.walk_len, self.window, self.batch_size, self.neg = walk_len, window, batch_size, neg
+        self.metapath, self.walks_per_node = tuple(metapath), walks_per_node
+        self.gen = torch.Generator(device=self.graph.device).manual_seed(seed)
+
+    def start_nodes(self) -> torch.Tensor:
+        ids = self.graph.types[self.metapath[0]][0]
+        perm = torch.randperm(ids.numel(), device=ids.device, generator=self.gen)
+        return ids[perm].repeat(self.walks_per_node)
+
+    def pairs(self):
+        walks, lens = self.graph.random_walk(self.start_nodes(), self.walk_len, self.metapath, generator=self.gen)
+        return walk_pairs(walks, lens, self.window)
+
+    def all_keys(self) -> torch.Tensor:
+        """Every node id (for the feed pass)."""
+        return torch.unique(torch.cat([t[0] for t in self.graph.types.values()]))
+
+    def batches(self) -> Iterator:
+        from .ops.pull_box_sparse import SlotBatch
+        dev = self.graph.device
+        c, x = self.pairs()
+        ids = self.graph.types[self.metapath[-1]][0]
+        P = c.numel()
+        if self.neg:
+            nc = c.repeat(self.neg)
+            nx = ids[torch.randint(ids.numel(), (P * self.neg,), device=dev, generator=self.gen)]
+            c, x = torch.cat([c, nc]), torch.cat([x, nx])
+        label = torch.zeros(c.numel(), device=dev)
+        label[:P] = 1.0
+        perm = torch.randperm(c.numel(), device=dev, generator=self.gen)
+        c, x, label = c[perm], x[perm], label[perm]
+        B = self.batch_size
+        for b in range(0, c.numel() - B + 1, B):
+            keys = torch.cat([c[b:b + B], x[b:b + B]])             # slot-major: slot 0 bags, then slot 1
+            lod = torch.arange(2 * B + 1, dtype=torch.int32, device=dev)
+            yield SlotBatch(keys, lod, B, 2, label[b:b + B, None].contiguous(), n_keys=2 * B)
+
+
+class GraphGpuWrapper:
+    """The reference's method names over ``GraphTable`` / ``DeviceGraph``
+    (graph_gpu_wrapper.h:34-99)."""
+    _ins = None
+
+    @classmethod
+    def get_instance(cls) -> "GraphGpuWrapper":
+        if cls._ins is None:
+            cls._ins = cls()
+        return cls._ins
+
+    def __init__(self):
+        self.table = GraphTable()
+        self.edge_types: dict = {}
+        self.device_graph: DeviceGraph | None = None
+
+    def set_up_types(self, edge_types: Sequence[str], node_types: Sequence[str] = ()) -> None:
+        self.edge_types = {name: i for i, name in enumerate(edge_types)}
+
+    def load_edge_file(self, name: str, filepath: str, reverse: bool = False) -> int:
+        t = self.edge_types.setdefault(name, len(self.edge_types))
+        return self.table.load_edge_file(filepath, t, reverse)
+
+    def upload_batch(self, device=None) -> DeviceGraph:
+        """Build every edge type and place it in HBM."""
+        for t in self.edge_types.values():
+            self.table.build(t)
+        self.device_graph = self.table.to_device(device, list(self.edge_types.values()))
+        return self.device_graph
+
+    def get_all_id(self, name: str) -> np.ndarray:
+        return self.table.all_ids(self.edge_types[name])
+
+    def graph_neighbor_sample(self, name: str, nodes, sample_size: int):
+        t = self.edge_types[name]
+        if self.device_graph is not None and torch.is_tensor(nodes):
+            return self.device_graph.sample_neighbors(nodes, sample_size, t)
+        return self.table.sample_neighbors(nodes, sample_size, t)
+
+    def finalize(self) -> None:
+        self.device_graph = None
+        self.table = GraphTable()
+        self.edge_types = {}

@@ -1,0 +1,115 @@
+"""Graph engine: CSR build, host / device sampling and walks, skip-gram training on walk pairs."""
+import numpy as np
+import torch
+
+from paddlebox_b200.graph import DeviceGraph, GraphDataGenerator, GraphGpuWrapper, GraphTable, walk_pairs
+
+
+def _two_cliques(n=12):
+    """Nodes 100..100+n-1 and 200..200+n-1, each group fully connected, one bridge 100 <-> 200."""
+    src, dst = [], []
+    for base in (100, 200):
+        for a in range(n):
+            for b in range(n):
+                if a != b:
+                    src.append(base + a)
+                    dst.append(base + b)
+    src += [100, 200]
+    dst += [200, 100]
+    return np.array(src, np.uint64), np.array(dst, np.uint64)
+
+
+def test_csr_sampling_and_walks_host_and_device(tmp_path):
+    src, dst = _two_cliques()
+    g = GraphTable()
+    g.add_edges(src, dst)
+    g.build()
+    ids, rp, col = g.csr()
+    assert g.num_nodes() == 24 and g.num_edges() == src.size and np.all(np.diff(ids.astype(np.int64)) > 0)
+    adj = {}
+    for a, b in zip(src.tolist(), dst.tolist()):
+        adj.setdefault(a, set()).add(b)
+    for i, node in enumerate(ids.tolist()):
+        assert set(ids[col[rp[i]:rp[i + 1]]].tolist()) == adj[node]
+    # host sampling: without replacement, inside the neighbourhood, all of it when k >= degree
+    nb, cnt = g.sample_neighbors(ids, 5, seed=3)
+    for node, row, c in zip(ids.tolist(), nb, cnt):
+        assert c == 5 and len(set(row.tolist())) == 5 and set(row.tolist()) <= adj[node]
+    nb, cnt = g.sample_neighbors(np.array([105, 999], np.uint64), 20)
+    assert cnt.tolist() == [11, 0] and set(nb[0, :11].tolist()) == adj[105] and not nb[1].any()
+    # walks follow edges; an unknown start ends at once
+    walks, lens = g.random_walk(np.array([100, 207, 999], np.uint64), 10, seed=1)
+    assert lens.tolist() == [10, 10, 1] and walks[2, 1:].sum() == 0
+    for w in walks[:2]:
+        assert all(int(b) in adj[int(a)] for a, b in zip(w[:-1], w[1:]))
+    # device twin (CPU tensors here; the same ops run on a GPU)
+    dg = g.to_device("cpu")
+    q = torch.tensor([100, 105, 999, 211], dtype=torch.int64)
+    assert dg.degree(q).tolist() == [12, 11, 0, 11]
+    gen = torch.Generator().manual_seed(0)
+    nb, cnt = dg.sample_neighbors(q, 4, generator=gen)
+    assert cnt.tolist() == [4, 4, 0, 4] and not nb[2].any()
+    assert all(set(r.tolist()) <= adj[int(n)] for n, r in zip(q.tolist(), nb) if int(n) in adj)
+    nb, cnt = dg.sample_neighbors(q, 16, generator=gen)
+    assert cnt.tolist() == [12, 11, 0, 11] and set(nb[1, :11].tolist()) == adj[105] and not nb[1, 11:].any()
+    walks, lens = dg.random_walk(q, 7, generator=gen)
+    assert lens.tolist() == [7, 7, 1, 7]
+    for w, l in zip(walks.tolist(), lens.tolist()):
+        assert all(b in adj[a] for a, b in zip(w[:l - 1], w[1:l])) and not any(w[l:])
+    c, x = walk_pairs(walks, lens, window=2)
+    assert c.numel() == x.numel() == 3 * (2 * (7 * 2) - 2 * 3)          # 3 full walks, window 2
+    # metapath over two edge types + the reference's wrapper names
+    f1, f2 = tmp_path / "u2i.txt", tmp_path / "i2u.txt"
+    f1.write_text("".join(f"{u}\t{1000 + u % 3}\n" for u in range(1, 10)))
+    w = GraphGpuWrapper()
+    w.set_up_types(["u2i", "i2u"])
+    assert w.load_edge_file("u2i", str(f1)) == 9 and w.load_edge_file("i2u", str(f1), reverse=True) == 9
+    dgraph = w.upload_batch("cpu")
+    assert sorted(w.get_all_id("u2i").tolist()) == list(range(1, 10)) + [1000, 1001, 1002]
+    walks, lens = dgraph.random_walk(torch.arange(1, 10), 5, metapath=(0, 1), generator=gen)
+    assert lens.tolist() == [5] * 9
+    assert torch.all(walks[:, 1::2] >= 1000) and torch.all(walks[:, 0::2] < 1000)
+    assert torch.all((walks[:, 0] % 3) == (walks[:, 2] % 3))           # users sharing an item
+    hw, hl = w.table.random_walk(np.arange(1, 10, dtype=np.uint64), 5, metapath=(0, 1))
+    assert np.all(hl == 5) and np.all(hw[:, 1::2] >= 1000)
+    nb, cnt = w.graph_neighbor_sample("i2u", np.array([1000], np.uint64), 2)
+    assert cnt[0] == 2 and all(int(v) % 3 == 0 for v in nb[0])
+
+
+def test_skipgram_trains_on_walk_pairs():
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    from paddlebox_b200.models.graph import SkipGram
+    from paddlebox_b200.trainer import CTRTrainer, TrainerConfig
+    BoxWrapper.reset_instance()
+    box = BoxWrapper.set_instance(embedx_dim=8, device=torch.device("cpu"), rank=0, world_size=1)
+    try:
+        box.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0, "mf_initial_range": 0.3,
+                                           "mf_learning_rate": 0.2, "learning_rate": 0.05})
+        src, dst = _two_cliques()
+        g = GraphTable()
+        g.add_edges(src, dst)
+        g.build()
+        gen = GraphDataGenerator(g, walk_len=6, window=2, batch_size=256, neg=2, walks_per_node=4, seed=1,
+                                 device="cpu")
+        box.begin_feed_pass("20240101")
+        box.feed_pass(gen.all_keys())
+        box.end_feed_pass()
+        box.begin_pass()
+        torch.manual_seed(0)
+        tr = CTRTrainer(SkipGram(8), box, TrainerConfig(dense_lr=1e-2))
+        losses = []
+        for _ in range(12):
+            for batch in gen.batches():
+                losses.append(float(tr.train_step(batch).detach()))
+        assert np.mean(losses[-10:]) < 0.8 * np.mean(losses[:10]), (losses[:3], losses[-3:])
+        # nodes of one clique ended up closer to each other than to the other clique
+        ids = torch.arange(100, 112).tolist() + torch.arange(200, 212).tolist()
+        vals, restore = box.pull_sparse(torch.tensor(ids, dtype=torch.int64))
+        emb = torch.nn.functional.normalize(vals[restore.long()][:, 3:11], dim=1)
+        sim = emb @ emb.T
+        inside = (sim[:12, :12].sum() - 12 + sim[12:, 12:].sum() - 12) / (2 * 12 * 11)
+        across = sim[:12, 12:].mean()
+        assert inside > across + 0.05, (float(inside), float(across))
+        box.end_pass()
+    finally:
+        BoxWrapper.reset_instance()
