@@ -36,6 +36,10 @@ class HostTable {
   PbxSparseOptConfig cfg;
   uint64_t seed;
   bool test_mode = false;
+  // > 0: serving-format saves (modes 1, 2) write embedx as int16 steps of this size and serving loads
+  // multiply back — the quantised feature layout of the reference's pull records
+  // (EmbedxQuantOp: value = int16 * scale, fleet/box_wrapper.cu:36-43)
+  float serving_quant_scale = 0.f;
 
   struct Shard {
     std::unordered_map<uint64_t, uint32_t> index;
@@ -443,7 +447,14 @@ class HostTable {
         fprintf(fp, " %d %d", (int)row[L.off_tail + 1], has_mf ? D : 0);
         if (has_mf) {
           if (!serving) for (int j = 0; j < L.embedx_state; ++j) fprintf(fp, " %.9g", row[L.off_xs + j]);
-          for (int j = 0; j < D; ++j) fprintf(fp, " %.9g", row[3 + j]);
+          if (serving && serving_quant_scale > 0.f) {
+            for (int j = 0; j < D; ++j) {
+              float q = std::nearbyint(row[3 + j] / serving_quant_scale);
+              fprintf(fp, " %d", (int)std::min(32767.f, std::max(-32768.f, q)));
+            }
+          } else {
+            for (int j = 0; j < D; ++j) fprintf(fp, " %.9g", row[3 + j]);
+          }
         }
         fputc('\n', fp);
         ++total;
@@ -492,7 +503,8 @@ class HostTable {
         if (!serving) for (int j = 0; j < L.embedx_state; ++j) row[L.off_xs + j] = f[q++];
         else if (L.optimizer == PBX_OPT_ADAM) { row[L.off_xs + 2 * D] = cfg.mf_beta1_decay_rate; row[L.off_xs + 2 * D + 1] = cfg.mf_beta2_decay_rate; }
         else if (L.optimizer == PBX_OPT_SHARED_ADAM) { row[L.off_xs + 2] = cfg.mf_beta1_decay_rate; row[L.off_xs + 3] = cfg.mf_beta2_decay_rate; }
-        for (int j = 0; j < D; ++j) row[3 + j] = f[q++];
+        const float dq = (serving && serving_quant_scale > 0.f) ? serving_quant_scale : 1.f;
+        for (int j = 0; j < D; ++j) row[3 + j] = f[q++] * dq;
       }
       ++cnt;
     }
@@ -559,6 +571,7 @@ int pbh_table_destroy(void* h) { delete (HostTable*)h; return 0; }
 int64_t pbh_table_size(void* h) { return (int64_t)((HostTable*)h)->size(); }
 int pbh_table_set_config(void* h, const PbxSparseOptConfig* cfg) { ((HostTable*)h)->cfg = *cfg; return 0; }
 int pbh_table_set_test_mode(void* h, int on) { ((HostTable*)h)->test_mode = on != 0; return 0; }
+int pbh_table_set_serving_quant(void* h, float scale) { ((HostTable*)h)->serving_quant_scale = scale; return 0; }
 int pbh_table_clear(void* h) { ((HostTable*)h)->clear(); return 0; }
 int pbh_table_fetch_rows(void* h, const uint64_t* keys, int64_t n, float* out, int create) {
   ((HostTable*)h)->fetch_rows(keys, n, out, create != 0, table_pool());

@@ -74,6 +74,9 @@ int64_t pbh_table_size(void* t);
 int pbh_table_set_config(void* t, const PbxSparseOptConfig* cfg);
 int pbh_table_set_test_mode(void* t, int on);
 int pbh_table_clear(void* t);
+/* scale > 0: serving saves (modes 1, 2) store embedx as int16 multiples of `scale`, serving loads
+ * dequantise (quantised feature layout, fleet/box_wrapper.cu:36-43); 0 turns it off */
+int pbh_table_set_serving_quant(void* t, float scale);
 int pbh_table_fetch_rows(void* t, const uint64_t* keys, int64_t n, float* out, int create);
 int pbh_table_store_rows(void* t, const uint64_t* keys, int64_t n, const float* rows, int mark_dirty);
 int pbh_table_pull(void* t, const uint64_t* keys, int64_t n, float* out, int out_stride);

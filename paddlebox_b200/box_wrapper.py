@@ -83,9 +83,11 @@ class BoxWrapper:
     def __init__(self, embedx_dim: int = 8, expand_embed_dim: int = 0, feature_type: int = 0,
                  pull_embedx_scale: float = 1.0, *, optimizer: str = "adagrad", device: torch.device | None = None,
                  rank: int | None = None, world_size: int | None = None, group=None):
-        """``feature_type``: 0 = fp32 embedx (HeterPS layout), 1 = adam, 2 = shared adam —
-        the closed library's other layouts (int16 quant / nncross / variable) are expressed
-        through ``optimizer`` and ``expand_embed_dim`` here."""
+        """``feature_type``: 0 = fp32 embedx (HeterPS layout), 1 = adam, 2 = shared adam, 3 = quant:
+        the serving models (``save_base`` xbox part, ``save_delta``) hold embedx as int16 multiples of
+        ``pull_embedx_scale`` and training pools on that grid (``seqpool_quant_ratio``), while the
+        table keeps fp32 master weights.  nncross = ``expand_embed_dim`` trailing embedx columns;
+        per-slot embedding widths = one table per width (``MultiDimBox``)  (SURVEY §9.10)."""
         self.embedx_dim = embedx_dim
         self.expand_embed_dim = expand_embed_dim
         self.feature_type = feature_type
@@ -149,6 +151,8 @@ class BoxWrapper:
         self.lr_map = dict(lr_map or {})
         self.max_keys_per_batch = int(max_keys_per_batch)
         self.host_table = HostTable(self.embedx_dim, self.optimizer, self.config, seed=self.rank)
+        if self.feature_type == 3:
+            self.host_table.set_serving_quant(self.pull_embedx_scale)
         if ssd_dir:
             self.host_table.ssd_open(os.path.join(ssd_dir, f"rank{self.rank:03d}"))
             self._ssd = True
@@ -173,6 +177,12 @@ class BoxWrapper:
         if model_path:
             self.load_model(model_path)
         self._initialized = True
+
+    @property
+    def seqpool_quant_ratio(self) -> int:
+        """``quant_ratio`` for ``fused_seqpool_cvm`` that puts pooled embedx on the serving grid
+        (0 unless ``feature_type`` 3)."""
+        return int(round(1.0 / self.pull_embedx_scale)) if self.feature_type == 3 and self.pull_embedx_scale > 0 else 0
 
     # ---- pass lifecycle ------------------------------------------------------------------
     def set_date(self, date: str) -> None:

@@ -68,6 +68,10 @@ class HostTable:
     def set_test_mode(self, on: bool) -> None:
         N.hcheck(N.host().pbh_table_set_test_mode(self._h, int(on)))
 
+    def set_serving_quant(self, scale: float) -> None:
+        """``scale`` > 0: serving-format saves hold embedx as int16 multiples of ``scale``."""
+        N.hcheck(N.host().pbh_table_set_serving_quant(self._h, C.c_float(scale)))
+
     def clear(self) -> None:
         N.hcheck(N.host().pbh_table_clear(self._h))
 

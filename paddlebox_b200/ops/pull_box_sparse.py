@@ -85,15 +85,21 @@ class _PullBoxSparse(torch.autograd.Function):
         n = batch.N
         hidden = box.hidden
         width = size - 0
+        quant = box.feature_type == 3          # int16 pull records: embedx = int16 * scale (box_wrapper.cu:36-43)
+        scale = 1.0 if quant else box.pull_embedx_scale
         if keys.is_cuda:
             out = torch.empty(max(n, 1), hidden - offset, dtype=torch.float32, device=keys.device)
             N.check(N.cuda().pbx_pull_scatter(N.ptr(vals), vals.stride(0), N.ptr(restore), C.c_int64(n), hidden,
-                                              offset, C.c_float(box.pull_embedx_scale), N.ptr(out), N.stream_ptr()))
+                                              offset, C.c_float(scale), N.ptr(out), N.stream_ptr()))
             out = out[:n]
         else:
             out = vals[restore.long()][:, offset:hidden].clone()
-            if box.pull_embedx_scale != 1.0:
-                out[:, max(3 - offset, 0):] *= box.pull_embedx_scale
+            if scale != 1.0:
+                out[:, max(3 - offset, 0):] *= scale
+        if quant:
+            ex = out[:, max(3 - offset, 0):]
+            q = box.pull_embedx_scale
+            ex.copy_(torch.round(ex / q).clamp_(-32768, 32767) * q)
         ctx.box, ctx.batch, ctx.restore, ctx.offset = box, batch, restore, offset
         return out
 

@@ -173,3 +173,58 @@ def test_psgpu_sparse_sgd_setters_reach_the_table(box):
     w.host_table.push(keys, push)
     after = w.host_table.fetch_rows(keys, create=False)
     assert abs((after[0, 2] - before[0, 2]) - 0.2) < 1e-5
+
+
+def test_quant_feature_type_serving_models_and_pull(tmp_path):
+    """feature_type 3: serving saves hold int16 embedx steps, serving loads dequantise, the batch model
+    keeps fp32, and pull_box_sparse returns embedx on the int16 grid."""
+    import os
+    import numpy as np
+    import torch
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    from paddlebox_b200.ops.pull_box_sparse import SlotBatch, pull_box_sparse
+    BoxWrapper.reset_instance()
+    scale = 1.0 / 256
+    box = BoxWrapper.set_instance(embedx_dim=4, feature_type=3, pull_embedx_scale=scale, device=torch.device("cpu"),
+                                  rank=0, world_size=1)
+    try:
+        box.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0})
+        assert box.seqpool_quant_ratio == 256
+        keys = np.arange(1, 41, dtype=np.uint64)
+        rows = box.host_table.fetch_rows(keys)
+        L = box.host_table.layout
+        rs = np.random.RandomState(0)
+        rows[:, 3:7] = rs.uniform(-1, 1, (40, 4)).astype(np.float32)
+        rows[:, L.off_mf] = 4
+        rows[:, 0] = 20
+        box.host_table.store_rows(keys, rows, mark_dirty=True)
+        box.save_base(str(tmp_path / "batch"), str(tmp_path / "xbox"))
+        line = open(os.path.join(tmp_path / "xbox", sorted(os.listdir(tmp_path / "xbox"))[0])).readline().split()
+        body = [f for name in sorted(os.listdir(tmp_path / "xbox")) for f in open(tmp_path / "xbox" / name)]
+        assert len(body) == 40
+        for ln in body:
+            tail = ln.split()[-4:]
+            assert all(t.lstrip("-").isdigit() and -32768 <= int(t) <= 32767 for t in tail), ln
+        from paddlebox_b200.host import HostTable
+        t2 = HostTable(4, "adagrad", box.config)
+        t2.set_serving_quant(scale)
+        assert t2.load(str(tmp_path / "xbox"), serving=True) == 40
+        got = t2.fetch_rows(keys, create=False)[:, 3:7]
+        assert np.abs(got - rows[:, 3:7]).max() <= scale / 2 + 1e-7
+        assert np.allclose(got / scale, np.round(got / scale), atol=1e-4)
+        t3 = HostTable(4, "adagrad", box.config)                       # the batch model is full precision
+        assert t3.load(str(tmp_path / "batch")) == 40
+        assert np.allclose(t3.fetch_rows(keys, create=False)[:, 3:7], rows[:, 3:7], rtol=1e-6)
+        # pull records on the grid
+        box.begin_feed_pass("20240101")
+        box.feed_pass(keys)
+        box.end_feed_pass()
+        box.begin_pass()
+        k = torch.from_numpy(keys.astype(np.int64))
+        lod = torch.arange(41, dtype=torch.int32)
+        emb = pull_box_sparse(SlotBatch(k, lod, 40, 1), box=box)
+        ex = emb[:, 3:].detach().numpy()
+        assert np.abs(ex - rows[:, 3:7]).max() <= scale / 2 + 1e-7 and np.allclose(ex / scale, np.round(ex / scale), atol=1e-4)
+        box.end_pass()
+    finally:
+        BoxWrapper.reset_instance()
