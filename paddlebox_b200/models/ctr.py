@@ -169,6 +169,30 @@ class MMoE(CTRModelBase):
         return loss, out
 
 
+class MultiDimDnn(nn.Module):
+    """DNN over slots of different embedding widths (``paddlebox_b200.multi_dim.MultiDimBox``:
+    the reference's variable-dimension pull layout, box_wrapper.cu:270-322)."""
+
+    def __init__(self, mbox, dense_dim: int = 0, hidden=(64, 32), seqpool_attrs: SeqpoolAttrs | None = None):
+        super().__init__()
+        self.mbox, self.dense_dim = mbox, dense_dim
+        self.attrs = seqpool_attrs or SeqpoolAttrs(use_cvm=True, cvm_offset=2)
+        self.sparse_width = sum(mbox.out_widths(self.attrs))
+        self.tower = FusedMLP([self.sparse_width + dense_dim, *hidden, 1], name="fc")
+
+    def mark_weights_dirty(self):
+        self.tower.mark_weights_dirty()
+
+    def forward(self, batch: SlotBatch):
+        label = batch.dense[:, 0].contiguous()
+        cvm = torch.stack([torch.ones_like(label), label], 1)
+        x = self.mbox.embedding_pool(batch, cvm, self.attrs)
+        if self.dense_dim:
+            x = torch.cat([x, batch.dense[:, 1:1 + self.dense_dim]], 1)
+        loss, pred = F.ctr_head(self.tower(x), label, tower_mod=self.tower)
+        return loss, {"pred": pred, "label": label}
+
+
 MODEL_REGISTRY = {"ctr_dnn": CtrDnn, "wide_deep": WideDeep, "deepfm": DeepFM, "mmoe": MMoE}
 
 

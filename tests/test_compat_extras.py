@@ -228,3 +228,68 @@ def test_quant_feature_type_serving_models_and_pull(tmp_path):
         box.end_pass()
     finally:
         BoxWrapper.reset_instance()
+
+
+def test_multi_dim_box_variable_embedding_widths(tmp_path):
+    """Slots of widths 4 / 8 / 4 / 8 / 16: split, per-width pull, columns in slot order, training,
+    checkpoint round trip."""
+    import numpy as np
+    import torch
+    from paddlebox_b200.models.ctr import MultiDimDnn
+    from paddlebox_b200.multi_dim import MultiDimBox
+    from paddlebox_b200.ops.pull_box_sparse import SlotBatch
+    from paddlebox_b200.ops.seqpool import SeqpoolAttrs
+    from paddlebox_b200.trainer import CTRTrainer, TrainerConfig
+    dims = [4, 8, 4, 8, 16]
+    mb = MultiDimBox(dims, device=torch.device("cpu"), rank=0, world_size=1)
+    mb.initialize({"mf_create_thresholds": 0.0, "mf_initial_range": 0.05})
+    gen = torch.Generator().manual_seed(0)
+    B, S = 48, 5
+    lens = torch.randint(0, 4, (S * B,), generator=gen)
+    lod = torch.zeros(S * B + 1, dtype=torch.int32)
+    lod[1:] = torch.cumsum(lens, 0)
+    slot_of = torch.repeat_interleave(torch.arange(S).repeat_interleave(B), lens)
+    keys = torch.randint(1, 60, (int(lod[-1]),), generator=gen, dtype=torch.int64) + 1000 * slot_of
+    dense = torch.zeros(B, 1)
+    first = keys[lod[:B].long().clamp(max=keys.numel() - 1)]
+    dense[:, 0] = (first % 2).float()
+    batch = SlotBatch(keys, lod, B, S, dense)
+    subs = mb.split(batch)
+    assert sorted(subs) == [4, 8, 16] and sum(s.N for s in subs.values()) == keys.numel()
+    for d, sub in subs.items():                       # every key went to the table of its slot's width
+        assert all(dims[int(k) // 1000] == d for k in sub.keys.tolist())
+        assert sub.lod.numel() == sub.num_slots * B + 1 and int(sub.lod[-1]) == sub.N
+    mb.begin_feed_pass("20240101")
+    mb.feed_pass_batch(batch)
+    mb.end_feed_pass()
+    mb.begin_pass()
+    # recognisable rows: embed_w = slot index
+    for d, box in mb.boxes.items():
+        ks = box._pass_keys[box._pass_keys != 0]
+        rows = box.host_table.fetch_rows(ks)
+        rows[:, 2] = (ks // 1000).astype(np.float32)
+        box.host_table.store_rows(ks, rows, mark_dirty=False)
+    attrs = SeqpoolAttrs(use_cvm=False, cvm_offset=2)
+    x = mb.embedding_pool(batch, torch.ones(B, 2), attrs)
+    widths = [1 + d for d in dims]
+    assert x.shape == (B, sum(widths))
+    off = 0
+    for s, w in enumerate(widths):                    # column block s holds slot s: pooled embed_w = s * bag length
+        bag = lens.view(S, B)[s].float()
+        assert torch.allclose(x[:, off].detach(), s * bag), s
+        off += w
+    torch.manual_seed(0)
+    tr = CTRTrainer(MultiDimDnn(mb, hidden=(16, 8)), mb.boxes[4], TrainerConfig(dense_lr=2e-2))
+    losses = [float(tr.train_step(batch).detach()) for _ in range(40)]
+    assert np.mean(losses[-5:]) < 0.9 * np.mean(losses[:5]), (losses[:3], losses[-3:])
+    mb.end_pass()
+    mb.save_base(str(tmp_path / "batch"), str(tmp_path / "xbox"))
+    mb2 = MultiDimBox(dims, device=torch.device("cpu"), rank=0, world_size=1)
+    mb2.initialize({"mf_create_thresholds": 0.0})
+    assert mb2.load_model(str(tmp_path / "batch")) == sum(b.host_table.size() for b in mb.boxes.values())
+    for d in mb.boxes:
+        ks = mb.boxes[d].host_table.keys()
+        assert np.allclose(mb2.boxes[d].host_table.fetch_rows(ks, create=False),
+                           mb.boxes[d].host_table.fetch_rows(ks, create=False), rtol=1e-5, atol=1e-7)
+    mb.finalize()
+    mb2.finalize()
