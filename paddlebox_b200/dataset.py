@@ -265,7 +265,8 @@ class InMemoryDataset(DatasetBase):
         self._native.local_shuffle(self._shuffle_seed)
 
     def set_shuffle_dir(self, path: str):
-        """Directory every rank can reach, used to exchange records in ``global_shuffle``."""
+        """Directory every rank can reach: ``global_shuffle`` then exchanges records through archive
+        files there instead of over the network."""
         self._shuffle_dir = path
 
     def global_shuffle(self, fleet=None, thread_num: int = 12, mode: str | None = None):
@@ -278,10 +279,11 @@ class InMemoryDataset(DatasetBase):
             from .parallel.shuffle import global_shuffle_records
             if mode is None:
                 mode = "search_id" if FLAGS.enable_shuffle_by_searchid else "random"
-            work = getattr(self, "_shuffle_dir", None) or os.path.join(tempfile.gettempdir(), "pbx_global_shuffle")
+            shared = getattr(self, "_shuffle_dir", None)
+            work = shared or os.path.join(tempfile.gettempdir(), "pbx_global_shuffle")
             self._shuffle_round = getattr(self, "_shuffle_round", 0) + 1
             global_shuffle_records(self, work, mode=mode, seed=self._shuffle_seed,
-                                   tag=f"shuffle{self._shuffle_round}")
+                                   tag=f"shuffle{self._shuffle_round}", transport="files" if shared else "network")
         self._native.local_shuffle(self._shuffle_seed)
 
     def slots_shuffle(self, slots: Sequence[str]):

@@ -225,6 +225,12 @@ def cpu_global_shuffle_and_cluster(rank, world):
     ds.set_shuffle_dir(os.path.join(base, "x"))
     ds.global_shuffle(mode="search_id")
     n_after = ds.get_memory_data_size()
+    # second round over the network transport (no shared directory): nothing lost either
+    ds._shuffle_dir = None
+    ds.global_shuffle(mode="random")
+    n_net = torch.tensor([ds.get_memory_data_size()])
+    dist.all_reduce(n_net)
+    assert int(n_net) == 240, int(n_net)
     c = Cluster.ins()
     total_before = c.allreduce(int(n_before), OP_SUM)
     total_after = c.allreduce(int(n_after), OP_SUM)
