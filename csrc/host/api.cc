@@ -157,6 +157,11 @@ int pbh_dataset_set_str(void* h, const char* key, const char* v) {
   else { pbh::set_error("unknown dataset option %s", key); return -1; }
   return 0;
 }
+int pbh_dataset_set_input_index(void* h, void* index) {
+  Dataset* d = (Dataset*)h;
+  d->input_index = index;           // the plugin's offset callback is bound when loading starts
+  return 0;
+}
 int pbh_dataset_load_into_memory(void* h) { return ((Dataset*)h)->load_into_memory(); }
 int pbh_dataset_preload_into_memory(void* h) { return ((Dataset*)h)->preload_into_memory(); }
 int pbh_dataset_wait_preload_done(void* h) { return ((Dataset*)h)->wait_preload_done(); }

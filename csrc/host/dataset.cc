@@ -14,6 +14,38 @@
 #include <cstdlib>
 #include <sstream>
 
+// ---- InputTable key index: string key -> row offset (0 = miss) ---------------------------------
+// (InputTable::GetIndexOffset / AddIndexData, fleet/box_wrapper.h:124-197)
+namespace {
+struct InputIndex {
+  std::mutex mu;
+  std::unordered_map<std::string, uint64_t> map;
+  std::atomic<uint64_t> miss{0};
+};
+}  // namespace
+extern "C" {
+int pbh_input_index_create(void** out) { *out = new InputIndex(); return 0; }
+int pbh_input_index_destroy(void* h) { delete (InputIndex*)h; return 0; }
+// offset of `key`, adding it at the next offset (1, 2, ...) when new; *fresh tells which
+uint64_t pbh_input_index_add(void* h, const char* key, size_t len, int* fresh) {
+  InputIndex* ix = (InputIndex*)h;
+  std::lock_guard<std::mutex> g(ix->mu);
+  auto r = ix->map.emplace(std::string(key, len), (uint64_t)ix->map.size() + 1);
+  if (fresh) *fresh = r.second ? 1 : 0;
+  return r.first->second;
+}
+uint64_t pbh_input_index_get(void* h, const char* key, size_t len) {
+  InputIndex* ix = (InputIndex*)h;
+  std::lock_guard<std::mutex> g(ix->mu);
+  auto it = ix->map.find(std::string(key, len));
+  if (it == ix->map.end()) { ++ix->miss; return 0; }
+  return it->second;
+}
+uint64_t pbh_input_index_size(void* h) { InputIndex* ix = (InputIndex*)h; std::lock_guard<std::mutex> g(ix->mu); return ix->map.size(); }
+uint64_t pbh_input_index_miss(void* h) { return ((InputIndex*)h)->miss.load(); }
+}
+static uint64_t pbh_input_index_get_cb(void* user, const char* key, size_t len) { return pbh_input_index_get(user, key, len); }
+
 namespace pbh {
 
 static thread_local std::string g_err;
@@ -184,11 +216,21 @@ int Dataset::finalize_slots() {
   // rebuild per-slot lookup
   slot_to_sparse_.assign(slots.size(), -1);
   for (size_t p = 0; p < sparse_idx_.size(); ++p) slot_to_sparse_[sparse_idx_[p]] = (int)p;
+  return bind_plugin();
+}
+
+// opens the parser plugin (once) and hands it the InputTable lookup when both exist
+int Dataset::bind_plugin() {
   if (!parser_plugin.empty() && !plugin_handle_) {
     plugin_handle_ = dlopen(parser_plugin.c_str(), RTLD_NOW | RTLD_LOCAL);
     PBH_REQUIRE(plugin_handle_ != nullptr, "cannot dlopen parser plugin %s: %s", parser_plugin.c_str(), dlerror());
     plugin_fn_ = dlsym(plugin_handle_, "pbx_parse_line");
     PBH_REQUIRE(plugin_fn_ != nullptr, "parser plugin %s lacks symbol pbx_parse_line", parser_plugin.c_str());
+  }
+  if (plugin_handle_ && input_index) {
+    // optional: void pbx_set_offset_func(uint64_t (*fn)(void* user, const char* key, size_t len), void* user)
+    typedef void (*set_fn_t)(uint64_t (*)(void*, const char*, size_t), void*);
+    if (auto set_fn = (set_fn_t)dlsym(plugin_handle_, "pbx_set_offset_func")) set_fn(&pbh_input_index_get_cb, input_index);
   }
   return 0;
 }
@@ -451,6 +493,7 @@ int Dataset::load_into_memory() {
     int rc = finalize_slots();
     if (rc) return rc;
   }
+  if (int rc = bind_plugin()) return rc;
   Timer t;
   t.start();
   chan_.open();

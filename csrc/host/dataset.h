@@ -181,6 +181,14 @@ class Dataset {
   double load_seconds_ = 0, merge_seconds_ = 0;
   void* plugin_handle_ = nullptr;
   void* plugin_fn_ = nullptr;
+  int bind_plugin();
+
+ public:
+  // string key -> row offset index of the InputTable (pbh_input_index_*); when set, a parser plugin
+  // that exports pbx_set_offset_func receives the lookup callback (GetOffsetFunc, data_feed.cc:4487)
+  void* input_index = nullptr;
+
+ private:
 };
 
 // reference compute_batch_num (data_set.cc:280-331): every worker gets the same number of batches

@@ -86,6 +86,18 @@ int pbh_table_save(void* t, const char* dir, int mode, int part_shard_base, floa
                    float delta_threshold, int clear_dirty, int64_t* n_saved);
 int pbh_table_load_file(void* t, const char* path, int serving, int64_t* n_loaded);
 int64_t pbh_table_keys(void* t, uint64_t* out, int64_t max_n);
+
+/* InputTable key index: string key -> row offset, 0 = miss (InputTable::AddIndexData / GetIndexOffset,
+ * fleet/box_wrapper.h:124-197).  Attached to a dataset, a parser plugin that also exports
+ *   void pbx_set_offset_func(uint64_t (*fn)(void* user, const char* key, size_t len), void* user)
+ * gets the lookup as its parse-time callback (GetOffsetFunc, data_feed.cc:4487-4492). */
+int pbh_input_index_create(void** out);
+int pbh_input_index_destroy(void* ix);
+uint64_t pbh_input_index_add(void* ix, const char* key, size_t len, int* fresh);
+uint64_t pbh_input_index_get(void* ix, const char* key, size_t len);
+uint64_t pbh_input_index_size(void* ix);
+uint64_t pbh_input_index_miss(void* ix);
+int pbh_dataset_set_input_index(void* ds, void* ix);
 /* SSD tier (closed-library LoadSSD2Mem / CheckNeedLimitMem, fleet/box_wrapper.cc:1316-1324): cold rows
  * move to one append-only file per shard under `dir`; a lookup that misses host memory promotes the
  * row back.  spill: rows unseen for >= min_unseen_days (negative: ignore age), then — if

@@ -474,6 +474,8 @@ class InputTableDataset(PadBoxSlotDataset):
 
     def load_into_memory(self):
         self.load_index_into_memory()
+        # a parser plugin that exports pbx_set_offset_func resolves string keys at parse time
+        self._native.set_input_index(self.input_table.handle)
         super().load_into_memory()
 
 

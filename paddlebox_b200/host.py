@@ -310,6 +310,10 @@ class NativeDataset:
         else:
             N.hcheck(lib.pbh_dataset_set_int(self._h, key.encode(), C.c_int64(int(value))))
 
+    def set_input_index(self, index_handle):
+        """Attach an ``InputTable`` key index (parse-time ``GetOffsetFunc`` for parser plugins)."""
+        N.hcheck(N.host().pbh_dataset_set_input_index(self._h, index_handle))
+
     def load_into_memory(self):
         N.hcheck(N.host().pbh_dataset_load_into_memory(self._h), "load_into_memory")
 

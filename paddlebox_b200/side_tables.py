@@ -66,19 +66,48 @@ class GpuReplicaCache:
 
 
 class InputTable:
+    """Host ``string -> row`` side table (``InputTable``, fleet/box_wrapper.h:124-197).  The key
+    index is native (``pbh_input_index_*``) so that parser plugins can resolve keys at parse time
+    (``GetOffsetFunc``); the rows are gathered on the device by ``lookup_input``."""
+
     def __init__(self, dim: int):
+        import ctypes as C
+        from . import _native as N
         self.dim = dim
-        self._index: dict = {}
+        self._h = C.c_void_p()
+        lib = N.host()
+        N.hcheck(lib.pbh_input_index_create(C.byref(self._h)))
+        for fn in ("add", "get", "size", "miss"):
+            getattr(lib, f"pbh_input_index_{fn}").restype = C.c_uint64
+        self._lib = lib
         self._rows: list = [[0.0] * dim]       # row 0 = miss
         self._lock = threading.Lock()
         self._dev = None
-        self.miss = 0
+
+    def __del__(self):
+        try:
+            if self._h:
+                self._lib.pbh_input_index_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
+
+    @property
+    def handle(self):
+        return self._h
+
+    @property
+    def miss(self) -> int:
+        return int(self._lib.pbh_input_index_miss(self._h))
 
     def add_index_data(self, key: str, vec) -> None:
+        import ctypes as C
         assert len(vec) == self.dim
+        kb = key.encode()
+        fresh = C.c_int()
         with self._lock:
-            if key not in self._index:
-                self._index[key] = len(self._rows)
+            self._lib.pbh_input_index_add(self._h, kb, C.c_size_t(len(kb)), C.byref(fresh))
+            if fresh.value:
                 self._rows.append([float(v) for v in vec])
             self._dev = None
 
@@ -95,10 +124,9 @@ class InputTable:
         return n
 
     def get_index_offset(self, key: str) -> int:
-        off = self._index.get(key, 0)
-        if off == 0:
-            self.miss += 1
-        return off
+        import ctypes as C
+        kb = key.encode()
+        return int(self._lib.pbh_input_index_get(self._h, kb, C.c_size_t(len(kb))))
 
     def lookup_input(self, idx: torch.Tensor) -> torch.Tensor:
         """Rows for int64 offsets (op ``lookup_input``)."""

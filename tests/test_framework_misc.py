@@ -278,6 +278,65 @@ def test_input_table_dataset_loads_index_files(tmp_path):
         BoxWrapper.reset_instance()
 
 
+def test_parser_plugin_resolves_input_table_keys_at_parse_time(tmp_path):
+    """GetOffsetFunc: a plugin that exports pbx_set_offset_func turns the string key of every line into
+    the InputTable row offset while parsing; lookup_input then gathers the rows."""
+    import subprocess
+    import torch
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    from paddlebox_b200.dataset import DatasetFactory, dense_slot, sparse_slot
+    src = tmp_path / "plug.cc"
+    src.write_text(r'''
+#include <cstdint>
+#include <cstdlib>
+#include <cstring>
+static uint64_t (*g_off)(void*, const char*, size_t) = nullptr;
+static void* g_user = nullptr;
+extern "C" void pbx_set_offset_func(uint64_t (*fn)(void*, const char*, size_t), void* user) { g_off = fn; g_user = user; }
+extern "C" int pbx_parse_line(const char* line, size_t len, void* ctx,
+    void (*emit_u64)(void*, int, const uint64_t*, size_t), void (*emit_f32)(void*, int, const float*, size_t),
+    void (*emit_meta)(void*, const char*, uint64_t, uint32_t, uint32_t)) {
+  // format: "<label> <string key> <feasign>"
+  char* end = nullptr;
+  float label = strtof(line, &end);
+  const char* k = end + 1;
+  const char* ke = (const char*)memchr(k, ' ', line + len - k);
+  if (!ke || !g_off) return 1;
+  uint64_t off = g_off(g_user, k, (size_t)(ke - k));
+  uint64_t fea = strtoull(ke + 1, &end, 10);
+  emit_f32(ctx, 0, &label, 1);
+  emit_u64(ctx, 1, &off, 1);          // the offset; 0 (miss) is dropped like any zero feasign
+  emit_u64(ctx, 2, &fea, 1);
+  emit_meta(ctx, "", 0, 0, 0);
+  return 0;
+}''')
+    so = tmp_path / "plug.so"
+    subprocess.check_call(["g++", "-shared", "-fPIC", "-O1", "-o", str(so), str(src)])
+    BoxWrapper.reset_instance()
+    box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=0, world_size=1)
+    box.initialize_gpu_and_load_model({})
+    try:
+        (tmp_path / "index-0").write_text("qa\t1 2\nqb\t3 4\n")
+        (tmp_path / "d.txt").write_text("1 qb 11\n0 zz 12\n1 qa 13\n")
+        ds = DatasetFactory().create_dataset("InputTableDataset")
+        ds.set_use_var([dense_slot("label"), sparse_slot("input_off"), sparse_slot("a")])
+        ds._native.set("parser_plugin", str(so))
+        ds.set_batch_size(3)
+        ds.set_thread(1)
+        ds.set_input_table_dim(2)
+        ds.set_index_filelist([str(tmp_path / "index-0")])
+        ds.set_filelist([str(tmp_path / "d.txt")])
+        ds.load_into_memory()
+        assert ds.get_memory_data_size() == 3 and ds.input_table.miss == 1
+        ds._native.prepare_train(1, False, 0, 0)
+        offs = sorted(int(k) for k in ds.unique_keys().tolist() if int(k) in (1, 2))
+        assert offs == [1, 2]
+        rows = ds.input_table.lookup_input(torch.tensor([2, 0, 1]))
+        assert torch.allclose(rows, torch.tensor([[3., 4.], [0., 0.], [1., 2.]]))
+    finally:
+        BoxWrapper.reset_instance()
+
+
 def test_queue_dataset_streams_in_file_order(tmp_path):
     import torch
     from paddlebox_b200.dataset import DatasetFactory
