@@ -133,6 +133,36 @@ class DatasetBase:
     def set_trainer_num(self, n: int):
         self.trainer_num = n
 
+    def set_thread_num(self, thread_num: int):
+        """pybind name of ``set_thread`` (data_set_py.cc)."""
+        self.set_thread(thread_num)
+
+    def set_data_feed_desc(self, desc: str):
+        """Configure from the text form of a ``DataFeedDesc`` (what ``desc()`` prints; the reference
+        passes the serialized proto, data_feed.proto:18-57): batch size, pipe command, threads, slots."""
+        import re
+        m = re.search(r"batch_size:\s*(\d+)", desc)
+        if m:
+            self.set_batch_size(int(m.group(1)))
+        m = re.search(r'pipe_command:\s*"([^"]*)"', desc)
+        if m:
+            self.set_pipe_command(m.group(1))
+        m = re.search(r"thread_num:\s*(\d+)", desc)
+        if m:
+            self.set_thread(int(m.group(1)))
+        slots, used = [], []
+        for body in re.findall(r"slots\s*\{([^}]*)\}", desc):
+            f = dict(re.findall(r'(\w+):\s*"?([^\s"]+)"?', body))
+            is_float = f.get("type", "uint64") == "float"
+            dense = f.get("is_dense", "false").lower() == "true"
+            dim = int(f.get("shape", 1))
+            v = SlotVar(f["name"], "float32" if is_float else "int64", 0 if dense else 1, (-1, dim))
+            slots.append(v)
+            if f.get("is_used", "true").lower() == "true":
+                used.append(v)
+        if slots:
+            self.set_use_var(used, slots)
+
     def desc(self) -> str:
         """Text description of the feed configuration (``DataFeedDesc``, data_feed.proto:45-57)."""
         lines = [f"name: \"{type(self).__name__}\"", f"batch_size: {self.batch_size}",
@@ -161,7 +191,7 @@ class InMemoryDataset(DatasetBase):
         super().__init__()
         self.parse_ins_id = False
         self.parse_logkey = False
-        self.merge_by_lineid = False
+        self._merge_by_lineid = False
         self.fleet_send_batch_size = 1024
         self.queue_num = None
         self.fea_eval = False
@@ -183,13 +213,101 @@ class InMemoryDataset(DatasetBase):
     def set_merge_by_sid(self, v: bool):
         self.merge_by_sid = bool(v)
 
+    def set_shuffle_by_uid(self, v: bool):
+        """Global shuffle keeps the instances of one user (ins_id prefix) on one rank."""
+        self.shuffle_by_uid = bool(v)
+
+    def set_current_phase(self, phase: int):
+        """1 = join, 0 = update: PV-merged batches are dealt only in the join phase
+        (data_set.cc:2782-2783)."""
+        self.current_phase = int(phase)
+        if getattr(self, "_pv_merge", False):
+            self._native.set("enable_pv_merge", int(phase == 1))
+
+    def enable_pv_merge(self) -> bool:
+        return bool(getattr(self, "_pv_merge", False))
+
+    def preprocess_instance(self):
+        """Group instances into page views before a join-phase pass (``PreprocessInstance``)."""
+        if getattr(self, "_pv_merge", False):
+            self._native.set("enable_pv_merge", 1)
+
+    def postprocess_instance(self):
+        """Back to one instance per record after the join phase (``PostprocessInstance``)."""
+        self._native.set("enable_pv_merge", 0)
+
+    def merge_by_lineid(self) -> int:
+        """pybind name: apply the ins_id merge now (``MergeByInsId``)."""
+        return self.merge_by_ins_id()
+
+    def set_generate_unique_feasigns(self, generate_uni_feasigns: bool = True, shard_num: int = 1):
+        self.gen_uni_feasigns, self.local_shard_num = bool(generate_uni_feasigns), int(shard_num)
+
+    def generate_local_tables_unlock(self, table_id: int = 0, fea_dim: int = 0, read_thread_num: int = 1,
+                                     consume_thread_num: int = 1, shard_num: int | None = None) -> list:
+        """Unique feasigns of the loaded pass, split into ``shard_num`` local tables by ``key % shard_num``
+        (``GenerateLocalTablesUnlock``, data_set.cc:771-877).  Returns the list of key arrays."""
+        shard_num = shard_num or getattr(self, "local_shard_num", 1)
+        keys = self._native.unique_keys()
+        self.local_tables = [keys[keys % np.uint64(shard_num) == np.uint64(s)] for s in range(shard_num)]
+        return self.local_tables
+
+    def set_preload_thread_num(self, n: int):
+        self.preload_thread_num = int(n)
+
+    def create_channel(self):
+        """Channels live inside the native dataset and are opened by every load; kept for API parity."""
+
+    def create_readers(self):
+        """Readers = the batch dealing of ``prepare_train`` (``CreateReaders``)."""
+        if self._prepared_workers == 0 and self._native.num_records():
+            self.prepare_train(max(1, self.trainer_num), 0)
+
+    def destroy_readers(self):
+        self._prepared_workers = 0
+
+    def create_preload_readers(self):
+        """Preload readers are the native reader threads started by ``preload_into_memory``."""
+
+    def destroy_preload_readers(self):
+        self._native.wait_preload_done()
+
+    def dynamic_adjust_channel_num(self, channel_num: int, discard_remaining_ins: bool = False):
+        self.queue_num = int(channel_num)
+
+    def set_gpu_graph_mode(self, v: bool = True):
+        """Batches come from ``graph.GraphDataGenerator`` walks instead of files."""
+        self.gpu_graph_mode = bool(v)
+
+    def tdm_sample(self, tree_name: str, tree_path, tdm_layer_counts, start_sample_layer: int = 1,
+                   with_hierarchy: bool = False, seed: int = 0, id_slot: int = 0, branch: int = 2):
+        """Bind a TDM item tree to the dataset (``Dataset.tdm_sample``).  ``tree_path``: a file with one
+        item id per line (leaf order) or a sequence of item ids.  Returns ``sampler(item_ids) ->
+        (nodes, labels, mask)`` (``ops.tdm.tdm_sample`` with ``tdm_layer_counts`` negatives per layer),
+        to be applied to the ids of slot ``id_slot`` in the model's forward."""
+        from .ops.tdm import TDMTree, tdm_sample
+        if isinstance(tree_path, str):
+            with open(tree_path) as f:
+                items = [int(x) for x in f.read().split()]
+        else:
+            items = list(tree_path)
+        tree = TDMTree(items, branch)
+        gen = torch.Generator().manual_seed(seed)
+        self.tdm = {"name": tree_name, "tree": tree, "id_slot": id_slot, "with_hierarchy": with_hierarchy}
+
+        def sampler(item_ids: torch.Tensor):
+            g = gen if item_ids.device.type == "cpu" else None
+            return tdm_sample(tree.to(item_ids.device), item_ids, tdm_layer_counts, start_sample_layer, g)
+        return sampler
+
     def set_enable_pv_merge(self, v: bool):
+        self._pv_merge = bool(v)
         self._native.set("enable_pv_merge", int(v))
 
     def set_merge_by_lineid(self, merge_size: int = 2):
         """Instances sharing an ins_id are merged into one after loading (``MergeByInsId``,
         data_set.cc:1387-1581); needs ``set_parse_ins_id(True)``."""
-        self.merge_by_lineid = True
+        self._merge_by_lineid = True
         self.merge_size = merge_size
 
     def merge_by_ins_id(self) -> int:
@@ -242,18 +360,19 @@ class InMemoryDataset(DatasetBase):
     # pass data ---------------------------------------------------------------------------------
     def load_into_memory(self):
         self._native.load_into_memory()
-        if self.merge_by_lineid:
+        if self._merge_by_lineid:
             self.merge_by_ins_id()
         monitor.stat_set("STAT_total_feasign_num_in_mem", self._native.total_feasigns())
 
     def preload_into_memory(self, thread_num: int | None = None):
+        thread_num = thread_num or getattr(self, "preload_thread_num", None)
         if thread_num:
             self.set_thread(thread_num)
         self._native.preload_into_memory()
 
     def wait_preload_done(self):
         self._native.wait_preload_done()
-        if self.merge_by_lineid:
+        if self._merge_by_lineid:
             self.merge_by_ins_id()
         monitor.stat_set("STAT_total_feasign_num_in_mem", self._native.total_feasigns())
 
@@ -278,7 +397,8 @@ class InMemoryDataset(DatasetBase):
             import tempfile
             from .parallel.shuffle import global_shuffle_records
             if mode is None:
-                mode = "search_id" if FLAGS.enable_shuffle_by_searchid else "random"
+                mode = "search_id" if FLAGS.enable_shuffle_by_searchid else \
+                    "ins_id" if getattr(self, "shuffle_by_uid", False) else "random"
             shared = getattr(self, "_shuffle_dir", None)
             work = shared or os.path.join(tempfile.gettempdir(), "pbx_global_shuffle")
             self._shuffle_round = getattr(self, "_shuffle_round", 0) + 1

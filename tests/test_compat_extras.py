@@ -293,3 +293,65 @@ def test_multi_dim_box_variable_embedding_widths(tmp_path):
                            mb.boxes[d].host_table.fetch_rows(ks, create=False), rtol=1e-5, atol=1e-7)
     mb.finalize()
     mb2.finalize()
+
+
+def test_dataset_pybind_parity_methods_and_desc_roundtrip(tmp_path):
+    import numpy as np
+    from paddlebox_b200.dataset import DatasetFactory
+    from tests.util_data import slot_vars, write_files
+    ds = DatasetFactory().create_dataset("InMemoryDataset")
+    ds.set_use_var(slot_vars(3, 2))
+    ds.set_batch_size(8)
+    ds.set_thread_num(2)
+    text = ds.desc()
+    ds2 = DatasetFactory().create_dataset("InMemoryDataset")
+    ds2.set_data_feed_desc(text)
+    assert ds2.desc() == text and ds2.batch_size == 8 and ds2.thread_num == 2
+    ds2.set_filelist(write_files(str(tmp_path), n_files=1, lines_per_file=40, n_sparse=3, n_dense=2, key_space=30))
+    ds2.set_preload_thread_num(1)
+    ds2.create_channel(); ds2.create_preload_readers()
+    ds2.preload_into_memory(); ds2.destroy_preload_readers(); ds2.wait_preload_done()
+    assert ds2.get_memory_data_size() == 40 and ds2.thread_num == 1
+    ds2.set_generate_unique_feasigns(True, 4)
+    tabs = ds2.generate_local_tables_unlock(0, 8, 1, 1)
+    allk = np.concatenate(tabs)
+    assert len(tabs) == 4 and len(np.unique(allk)) == allk.size == ds2.unique_keys().size
+    assert all(np.all(t % np.uint64(4) == np.uint64(i)) for i, t in enumerate(tabs))
+    ds2.set_trainer_num(2)
+    ds2.create_readers()
+    assert ds2._prepared_workers == 2
+    ds2.destroy_readers()
+    ds2.set_current_phase(1); ds2.preprocess_instance(); ds2.postprocess_instance()
+    ds2.set_shuffle_by_uid(True); ds2.dynamic_adjust_channel_num(4); ds2.set_gpu_graph_mode(False)
+    assert ds2.enable_pv_merge() is False and callable(ds2.merge_by_lineid)
+
+
+def test_tdm_tree_and_sampling():
+    import torch
+    from paddlebox_b200.dataset import DatasetFactory
+    from paddlebox_b200.ops.tdm import TDMTree
+    items = [50, 10, 40, 20, 30, 60]                       # 6 leaves -> binary tree of height 4 (8 leaf slots)
+    tree = TDMTree(items, branch=2)
+    assert tree.height == 4 and tree.layer_size == [1, 2, 3, 6]
+    path = tree.travel(torch.tensor([50, 20, 999]))
+    assert path[0].tolist() == [1, 2, 4, 8] and path[1].tolist() == [1, 2, 5, 11] and path[2].tolist() == [0, 0, 0, 0]
+    kids, leaf = tree.children(torch.tensor([1, 3, 6, 0]))
+    assert kids.tolist() == [[2, 3], [6, 0], [12, 13], [0, 0]] and leaf.tolist() == [[False, False], [False, False], [True, True], [False, False]]
+    ds = DatasetFactory().create_dataset("InMemoryDataset")
+    sampler = ds.tdm_sample("t", items, [1, 2, 3], start_sample_layer=1, seed=3)
+    ids = torch.tensor([10, 60, 30, 999] * 50)
+    nodes, labels, mask = sampler(ids)
+    assert nodes.shape == labels.shape == mask.shape == (200, 3 + 6)
+    assert labels[0].tolist() == [1, 0, 1, 0, 0, 1, 0, 0, 0]
+    trav = tree.travel(ids)
+    col = 0
+    for l, neg in zip((1, 2, 3), (1, 2, 3)):
+        lo, size = tree.layer_start[l] + 1, tree.layer_size[l]
+        assert torch.equal(nodes[:, col], trav[:, l])
+        negs, m = nodes[:, col + 1:col + 1 + neg], mask[:, col + 1:col + 1 + neg].bool()
+        assert torch.all((negs[m] >= lo) & (negs[m] < lo + size))              # inside the layer
+        assert not torch.any(negs == trav[:, l:l + 1]) or not torch.any((negs == trav[:, l:l + 1]) & m)
+        col += 1 + neg
+    assert not mask[3].any() and mask[0, 0] == 1                             # unknown item: all masked
+    # layer 1 has 2 nodes: one negative available; layer 2 has 3 nodes: 2 negatives
+    assert mask[0].tolist() == [1, 1, 1, 1, 1, 1, 1, 1, 1]
