@@ -25,11 +25,22 @@ class AucCalculator {
   void reset() { std::lock_guard<std::mutex> g(mu_); reset_locked(); }
 
   // label in {0,1} (or a float in [0,1] when float_label); mask (nullable) selects rows
-  int add_data(const float* pred, const float* label, const float* mask, int64_t n, bool float_label) {
+  // float_label 2 = continuous values: error / mean sums only, nothing clamped or bucketed
+  // (add_unlock_data_with_continue_label, fleet/metrics.cc:98-105)
+  int add_data(const float* pred, const float* label, const float* mask, int64_t n, int float_label) {
     std::lock_guard<std::mutex> g(mu_);
     for (int64_t i = 0; i < n; ++i) {
       if (mask && mask[i] == 0.f) continue;
       double p = pred[i];
+      if (float_label == 2) {
+        double y = label[i];
+        abserr_ += std::fabs(p - y);
+        sqrerr_ += (p - y) * (p - y);
+        pred_sum_ += p;
+        label_sum_ += y;
+        total_ += 1;
+        continue;
+      }
       if (!(p >= 0.0 && p <= 1.0)) {   // also catches NaN
         if (std::isnan(p)) nan_cnt_ += 1; else if (std::isinf(p)) inf_cnt_ += 1;
         p = std::min(1.0, std::max(0.0, std::isnan(p) ? 0.0 : p));
@@ -175,7 +186,7 @@ int pbh_auc_create(void** out, int table_size) { *out = new AucCalculator(table_
 int pbh_auc_destroy(void* h) { delete (AucCalculator*)h; return 0; }
 int pbh_auc_reset(void* h) { ((AucCalculator*)h)->reset(); return 0; }
 int pbh_auc_add(void* h, const float* pred, const float* label, const float* mask, int64_t n, int float_label) {
-  return ((AucCalculator*)h)->add_data(pred, label, mask, n, float_label != 0);
+  return ((AucCalculator*)h)->add_data(pred, label, mask, n, float_label);
 }
 int pbh_auc_add_uid(void* h, const float* pred, const float* label, const uint64_t* uid, int64_t n) {
   ((AucCalculator*)h)->add_uid_data(pred, label, uid, n);

@@ -423,8 +423,67 @@ class BoxWrapper:
         the data-parallel group and resets the metric (box_wrapper.cc:1027-1046)."""
         return self._metrics[name].get_metric_msg(self.group if self.world_size > 1 else None)
 
+    def get_continue_metric_msg(self, name: str) -> list:
+        """[mae, rmse, actual value, predicted value, size] of a continuous-value metric
+        (``GetContinueMetricMsg``, box_wrapper.cc:1048-1065); resets it."""
+        m = self._metrics[name]
+        grp = self.group if self.world_size > 1 else None
+        if hasattr(m, "get_continue_msg"):
+            return m.get_continue_msg(grp)
+        msg = m.get_metric_msg(grp)
+        if len(msg) == 5:                       # ContinueMaskCalculator: [mae, rmse, predicted, actual, size]
+            return [msg[0], msg[1], msg[3], msg[2], msg[4]]
+        return [msg[2], msg[3], msg[4], msg[5], msg[7]]
+
     def get_nan_inf_metric_msg(self, name: str) -> list:
         return self._metrics[name].get_nan_inf_msg()
+
+    # ---- AUC runner / dataset glue (box_helper_py.cc) --------------------------------------------
+    def initialize_auc_runner(self, slot_eval, thread_num: int = 1, pool_size: int = 0, slot_list=()):
+        """``InitializeAucRunner`` (box_wrapper.cc:212-368): slot groups whose feasigns are shuffled
+        across instances to measure each group's contribution.  Returns the runner
+        (``auc_runner.AucRunner``), also kept as ``self.auc_runner``."""
+        from .auc_runner import AucRunner
+        FLAGS.padbox_auc_runner_mode = True
+        self.auc_runner = AucRunner(self, slot_eval, thread_num=thread_num, pool_size=pool_size, slot_list=slot_list)
+        return self.auc_runner
+
+    def set_dataset_name(self, name: str) -> None:
+        self.dataset_name = name
+
+    def set_input_table_dim(self, dim: int) -> None:
+        from .side_tables import InputTable
+        self.input_table = InputTable(int(dim))
+
+    def init_afs_api(self, fs_name: str, fs_ugi: str, conf_path: str = "") -> bool:
+        """``InitAfsAPI``: remote files are then reached through ``self.file_mgr`` (``BoxFileMgr``)."""
+        from .side_tables import BoxFileMgr
+        self.file_mgr = BoxFileMgr()
+        return self.file_mgr.init(fs_name, fs_ugi, conf_path)
+
+    def release_pool(self) -> None:
+        """``ReleasePool``: give cached host / device blocks back (record pools are freed by
+        ``dataset.release_memory``)."""
+        import gc
+        gc.collect()
+        if self.use_cuda:
+            torch.cuda.empty_cache()
+
+    def print_device_info(self) -> str:
+        """``PrintDeviceInfo``: one line per visible device with its memory use."""
+        lines = []
+        if self.use_cuda:
+            for d in range(torch.cuda.device_count()):
+                free, total = torch.cuda.mem_get_info(d)
+                lines.append(f"device {d}: {torch.cuda.get_device_name(d)} used {(total - free) >> 20} MiB of "
+                             f"{total >> 20} MiB")
+        else:
+            lines.append("device cpu")
+        if self.host_table is not None:
+            lines.append(f"host table rows {self.host_table.mem_rows()} (+ {self.host_table.ssd_rows()} on SSD)")
+        msg = "\n".join(lines)
+        print(msg)
+        return msg
 
     # ---- misc ---------------------------------------------------------------------------------
     def print_sync_timer(self) -> str:

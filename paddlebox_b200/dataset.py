@@ -549,6 +549,10 @@ class BoxPSDataset(InMemoryDataset):
     def wait_feed_pass_done(self):
         self.wait_preload_done()
 
+    def read_ins_into_memory(self):
+        """``BoxHelper::ReadData2Memory``: BeginFeedPass -> LoadIntoMemory -> EndFeedPass."""
+        self.load_into_memory()
+
 
 class PadBoxSlotDataset(BoxPSDataset):
     """SlotRecord dataset of PaddleBox (``PadBoxSlotDataset``, dataset.py:1363-1497)."""

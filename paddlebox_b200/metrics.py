@@ -184,10 +184,11 @@ class FloatMaskMetricMsg(MaskMetricMsg):
 
 class ContinueMaskMetricMsg(MaskMetricMsg):
     """Regression-style metric on masked rows: only mae / rmse / mean prediction / mean label
-    are meaningful (ContinueMaskCalculator)."""
+    are meaningful (ContinueMaskCalculator).  Values are unbounded: nothing is clamped to [0, 1]
+    (add_unlock_data_with_continue_label, fleet/metrics.cc:98-105)."""
 
     def __init__(self, **kw):
-        super().__init__(float_label=True, **kw)
+        super().__init__(float_label=2, **kw)
 
     def get_metric_msg(self, group=None):
         self._flush_device()

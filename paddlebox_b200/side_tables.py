@@ -172,6 +172,14 @@ class BoxFileMgr:
             return [ln.split()[-1] for ln in out if ln and not ln.startswith("Found")]
         return sorted(os.path.join(path, n) for n in os.listdir(path))
 
+    def list_info(self, path: str) -> list:
+        """[(path, size in bytes)] of the entries of ``path`` (``BoxFileMgr::list_info``)."""
+        if self._remote(path):
+            out = self._run("-ls", path).stdout.splitlines()
+            rows = [ln.split() for ln in out if ln and not ln.startswith("Found")]
+            return [(r[-1], int(r[4])) for r in rows if len(r) >= 8]
+        return [(p, os.path.getsize(p)) for p in sorted(os.path.join(path, n) for n in os.listdir(path))]
+
     def makedir(self, path: str) -> bool:
         if self._remote(path):
             return self._run("-mkdir", "-p", path).returncode == 0

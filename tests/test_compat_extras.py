@@ -355,3 +355,28 @@ def test_tdm_tree_and_sampling():
     assert not mask[3].any() and mask[0, 0] == 1                             # unknown item: all masked
     # layer 1 has 2 nodes: one negative available; layer 2 has 3 nodes: 2 negatives
     assert mask[0].tolist() == [1, 1, 1, 1, 1, 1, 1, 1, 1]
+
+
+def test_box_wrapper_pybind_parity_names(tmp_path):
+    import torch
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    BoxWrapper.reset_instance()
+    box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=0, world_size=1)
+    try:
+        box.initialize_gpu_and_load_model({})
+        box.init_metric("ContinueMaskCalculator", "c", "label", "pred", mask_varname="mask", metric_phase=1)
+        box.add_metric_data({"pred": torch.tensor([0.5, 2.0, 9.0]), "label": torch.tensor([1.0, 1.0, 0.0]),
+                             "mask": torch.tensor([1, 1, 0])})
+        mae, rmse, actual, predicted, size = box.get_continue_metric_msg("c")
+        assert size == 2 and abs(mae - 0.75) < 1e-6 and abs(actual - 1.0) < 1e-6 and abs(predicted - 1.25) < 1e-6
+        runner = box.initialize_auc_runner([["s1"], ["s2", "s3"]], thread_num=2, slot_list=["s1", "s2", "s3"])
+        assert runner.eval_slot_set() == {"s1", "s2", "s3"} and box.auc_runner is runner
+        box.set_dataset_name("train"); box.set_input_table_dim(3); box.release_pool()
+        assert box.input_table.dim == 3 and "host table rows" in box.print_device_info()
+        assert box.init_afs_api("", "", "") is True
+        (tmp_path / "a.txt").write_text("12345")
+        assert box.file_mgr.list_info(str(tmp_path)) == [(str(tmp_path / "a.txt"), 5)]
+    finally:
+        from paddlebox_b200.flags import FLAGS
+        FLAGS.padbox_auc_runner_mode = False
+        BoxWrapper.reset_instance()
