@@ -257,3 +257,9 @@ def fused_seqpool_cvm_with_pcoc(x: torch.Tensor, lod: torch.Tensor, batch_size: 
         out = pooled[:, cvm_offset:]
     E = out.shape[1]
     return out.view(num_slots, batch_size, E).permute(1, 0, 2).reshape(batch_size, num_slots * E)
+
+
+def cross_norm_layer_hadamard(fields_num: int, embed_dim: int, **kw) -> CrossNormHadamard:
+    """``fluid.contrib.layers.cross_norm_layer_hadamard`` (contrib/layers/nn.py): returns the layer
+    (parameters = the three data-norm summaries); call it on the ``[B, fields_num*2*embed_dim]`` input."""
+    return CrossNormHadamard(fields_num, embed_dim, **kw)

@@ -95,3 +95,22 @@ def tdm_sample(tree: TDMTree, item_ids: torch.Tensor, neg_per_layer: Sequence[in
         labels.append(torch.zeros(n, neg, dtype=torch.int64, device=dev))
         mask.append(ok.long())
     return torch.cat(nodes, 1), torch.cat(labels, 1), torch.cat(mask, 1)
+
+
+def tdm_child(x: torch.Tensor, tree: TDMTree):
+    """``fluid.contrib.layers.tdm_child`` (contrib/layers/nn.py): children of every node id in ``x``
+    and the mask of those that are items (leaves).  Shapes ``x.shape + [branch]``."""
+    kids, leaf = tree.children(x.reshape(-1))
+    return kids.view(*x.shape, tree.branch), leaf.view(*x.shape, tree.branch).long()
+
+
+def tdm_sampler(x: torch.Tensor, neg_samples_num_list: Sequence[int], tree: TDMTree, output_positive: bool = True,
+                output_list: bool = False, start_layer: int = 1, generator: torch.Generator | None = None):
+    """``fluid.contrib.layers.tdm_sampler``: per tree layer the positive node of every item in ``x``
+    plus ``neg_samples_num_list[layer]`` negatives.  Returns ``(out, labels, mask)``; with
+    ``output_list`` each is a list with one tensor per layer."""
+    nodes, labels, mask = tdm_sample(tree, x.reshape(-1), neg_samples_num_list, start_layer, generator, output_positive)
+    if not output_list:
+        return nodes, labels, mask
+    widths = [int(n) + (1 if output_positive else 0) for n in neg_samples_num_list[:tree.height - start_layer]]
+    return tuple(list(torch.split(t, widths, dim=1)) for t in (nodes, labels, mask))
