@@ -60,8 +60,15 @@ class BoxPSOptimizer:
         """Attach the trainer configuration to ``model`` (the "program"); returns the config.
         ``Executor.train_from_dataset(model, dataset)`` picks it up."""
         if self._cut_list:
-            raise NotImplementedError("pipeline-by-section (cut_list) is not used by BoxPSWorker in the reference "
-                                      "either (SURVEY §2.7); train the whole model on every GPU")
+            # pipeline-by-section (_split_program, optimizer.py:7496-7575): the model is cut after the
+            # named children; run the sections with model._section_pipeline.forward_backward(...)
+            from .parallel.pipeline import SectionPipeline, split_sequential
+            sections = split_sequential(model, self._cut_list)
+            places = self._place_list or None
+            if places is not None and len(places) != len(sections):
+                raise ValueError(f"place_list has {len(places)} entries for {len(sections)} sections")
+            model._section_pipeline = SectionPipeline(sections, places, self._concurrency_list or None,
+                                                      self._queue_size)
         cfg = TrainerConfig(dense_lr=self._optimizer.lr, dense_optimizer=self._optimizer.kind,
                             sync_dense_mode=self._mode, sync_weight_step=max(1, self._sync_steps),
                             async_mode=self._async, dump_thread_num=self._dump_thread_num)
