@@ -27,6 +27,48 @@ static inline float uniform01(uint64_t key, uint32_t idx, uint64_t seed) {
   return ((float)((x >> 40) + 1)) * (1.0f / 16777216.0f);
 }
 
+// key -> row number, open addressing with linear probing (load <= 0.5); an entry stores row + 1 so
+// that 0 marks an empty cell and key 0 needs no special case
+class FlatIndex {
+ public:
+  int64_t find(uint64_t key) const {
+    if (cells_.empty()) return -1;
+    for (size_t i = mix64(key) & mask_;; i = (i + 1) & mask_) {
+      const Cell& c = cells_[i];
+      if (c.row1 == 0) return -1;
+      if (c.key == key) return (int64_t)c.row1 - 1;
+    }
+  }
+  void emplace(uint64_t key, uint32_t row) {
+    if ((n_ + 1) * 2 > cells_.size()) grow();
+    put(key, row + 1);
+    ++n_;
+  }
+  void prefetch(uint64_t key) const {
+    if (!cells_.empty()) __builtin_prefetch(&cells_[mix64(key) & mask_]);
+  }
+  size_t size() const { return n_; }
+
+ private:
+  struct Cell { uint64_t key; uint32_t row1; };
+  void put(uint64_t key, uint32_t row1) {
+    size_t i = mix64(key) & mask_;
+    while (cells_[i].row1 != 0) i = (i + 1) & mask_;
+    cells_[i].key = key;
+    cells_[i].row1 = row1;
+  }
+  void grow() {
+    std::vector<Cell> old;
+    old.swap(cells_);
+    cells_.assign(old.empty() ? 1024 : old.size() * 2, Cell{0, 0});
+    mask_ = cells_.size() - 1;
+    for (const Cell& c : old)
+      if (c.row1) put(c.key, c.row1);
+  }
+  std::vector<Cell> cells_;
+  size_t mask_ = 0, n_ = 0;
+};
+
 class HostTable {
  public:
   HostTable(int embedx_dim, int optimizer, const PbxSparseOptConfig& cfg, uint64_t seed, int shards)
@@ -42,7 +84,7 @@ class HostTable {
   float serving_quant_scale = 0.f;
 
   struct Shard {
-    std::unordered_map<uint64_t, uint32_t> index;
+    FlatIndex index;
     std::vector<float> rows;
     std::vector<uint64_t> keys;
     std::vector<uint8_t> dirty;
@@ -259,9 +301,9 @@ class HostTable {
 
   float* find_or_create(uint64_t key, bool create, bool* fresh = nullptr) {
     Shard& s = shards_[shard_of(key)];
-    auto it = s.index.find(key);
+    int64_t at = s.index.find(key);
     if (fresh) *fresh = false;
-    if (it != s.index.end()) return s.rows.data() + (size_t)it->second * L.stride;
+    if (at >= 0) return s.rows.data() + (size_t)at * L.stride;
     if (!ssd_.empty()) {
       if (float* cold = promote(s, ssd_[shard_of(key)], key)) return cold;
     }
@@ -284,15 +326,15 @@ class HostTable {
       float* row = find_or_create(keys[i], create);
       if (row) memcpy(out + i * L.stride, row, L.stride * sizeof(float));
       else init_row(out + i * L.stride, keys[i]);
-    });
+    }, create);
   }
 
   void store_rows(const uint64_t* keys, int64_t n, const float* rows, bool mark_dirty, ThreadPool* pool) {
     run_sharded(keys, n, pool, [&](Shard& s, int64_t i) {
       float* row = find_or_create(keys[i], true);
       memcpy(row, rows + i * L.stride, L.stride * sizeof(float));
-      if (mark_dirty) s.dirty[s.index[keys[i]]] = 1;
-    });
+      if (mark_dirty) s.dirty[s.index.find(keys[i])] = 1;
+    }, true);
   }
 
   // CPU pull records [n, hidden] (key 0 / unknown keys -> zeros)
@@ -315,7 +357,7 @@ class HostTable {
       float* row = find_or_create(keys[i], false);
       if (!row) return;
       apply_push(row, keys[i], push + i * push_stride);
-      s.dirty[s.index[keys[i]]] = 1;
+      s.dirty[s.index.find(keys[i])] = 1;
     });
   }
 
@@ -531,22 +573,52 @@ class HostTable {
 
  private:
   template <typename F>
-  void run_sharded(const uint64_t* keys, int64_t n, ThreadPool* pool, F fn) {
+  void run_sharded(const uint64_t* keys, int64_t n, ThreadPool* pool, F fn, bool may_create = false) {
     const size_t S = shards_.size();
     if (!pool || n < 4096) {
       for (int64_t i = 0; i < n; ++i) fn(shards_[shard_of(keys[i])], i);
       return;
     }
-    // each worker owns a disjoint set of shards -> no locks on the maps
-    int W = pool->size();
-    pool->parallel_range((size_t)W, [&](size_t wb, size_t we, int) {
-      for (size_t w = wb; w < we; ++w)
-        for (int64_t i = 0; i < n; ++i) {
-          size_t sh = shard_of(keys[i]);
-          if (sh % (size_t)W == w) fn(shards_[sh], i);
-        }
+    // one parallel pass computes every key's shard, a counting sort groups the positions by shard, then
+    // each worker walks whole shards: no locks on the maps and every key is hashed once
+    std::vector<uint8_t> sh((size_t)n);
+    const int W = pool->size();
+    std::vector<std::vector<int64_t>> cnt(W, std::vector<int64_t>(S, 0));
+    pool->parallel_range((size_t)n, [&](size_t b, size_t e, int w) {
+      auto& c = cnt[w];
+      for (size_t i = b; i < e; ++i) { sh[i] = (uint8_t)shard_of(keys[i]); ++c[sh[i]]; }
     });
-    (void)S;
+    std::vector<int64_t> start(S + 1, 0);
+    for (size_t q = 0; q < S; ++q) {
+      int64_t t = 0;
+      for (int w = 0; w < W; ++w) t += cnt[w][q];
+      start[q + 1] = start[q] + t;
+    }
+    // position of (worker w, shard q)'s first element: workers scanned contiguous ranges in order
+    std::vector<std::vector<int64_t>> at(W, std::vector<int64_t>(S, 0));
+    for (size_t q = 0; q < S; ++q) {
+      int64_t t = start[q];
+      for (int w = 0; w < W; ++w) { at[w][q] = t; t += cnt[w][q]; }
+    }
+    std::vector<int64_t> order((size_t)n);
+    pool->parallel_range((size_t)n, [&](size_t b, size_t e, int w) {
+      auto& a = at[w];
+      for (size_t i = b; i < e; ++i) order[a[sh[i]]++] = (int64_t)i;
+    });
+    pool->parallel_range(S, [&](size_t qb, size_t qe, int) {
+      for (size_t q = qb; q < qe; ++q) {
+        Shard& shard = shards_[q];
+        if (may_create) {            // one growth step instead of repeated doubling while rows are added
+          size_t extra = (size_t)(start[q + 1] - start[q]);
+          if (shard.rows.capacity() < shard.rows.size() + extra * L.stride)
+            shard.rows.reserve(std::max(shard.rows.capacity() * 2, shard.rows.size() + extra * L.stride));
+        }
+        for (int64_t j = start[q]; j < start[q + 1]; ++j) {
+          if (j + 8 < start[q + 1]) shard.index.prefetch(keys[order[j + 8]]);
+          fn(shard, order[j]);
+        }
+      }
+    });
   }
   std::vector<Shard> shards_;
   std::vector<SsdShard> ssd_;
