@@ -87,6 +87,10 @@ int pbh_table_save(void* t, const char* dir, int mode, int part_shard_base, floa
 int pbh_table_load_file(void* t, const char* path, int serving, int64_t* n_loaded);
 int64_t pbh_table_keys(void* t, uint64_t* out, int64_t max_n);
 
+/* parallel sort + unique of keys in place (end of a feed pass: PSGPUWrapper::PreBuildTask,
+ * fleet/ps_gpu_wrapper.cc:114-335); returns the unique count */
+int64_t pbh_sort_unique_u64(uint64_t* keys, int64_t n);
+
 /* InputTable key index: string key -> row offset, 0 = miss (InputTable::AddIndexData / GetIndexOffset,
  * fleet/box_wrapper.h:124-197).  Attached to a dataset, a parser plugin that also exports
  *   void pbx_set_offset_func(uint64_t (*fn)(void* user, const char* key, size_t len), void* user)

@@ -201,7 +201,8 @@ class BoxWrapper:
     def end_feed_pass(self) -> None:
         """Dedup the pass's keys and route every key to the rank that owns it."""
         t0 = time.time()
-        keys = np.unique(np.concatenate(self._feed_keys)) if self._feed_keys else np.zeros(0, np.uint64)
+        from .host import sort_unique_u64
+        keys = sort_unique_u64(np.concatenate(self._feed_keys)) if self._feed_keys else np.zeros(0, np.uint64)
         self._feed_keys = []
         if self.world_size > 1:
             import torch.distributed as dist
@@ -211,7 +212,7 @@ class BoxWrapper:
             gathered = [None] * self.world_size
             dist.all_gather_object(gathered, [p.tobytes() for p in parts], group=self.group)
             mine = [np.frombuffer(g[self.rank], dtype=np.uint64) for g in gathered]
-            keys = np.unique(np.concatenate(mine)) if mine else np.zeros(0, np.uint64)
+            keys = sort_unique_u64(np.concatenate(mine)) if mine else np.zeros(0, np.uint64)
         self._pass_keys = keys
         self.timers.add("feed_pass", time.time() - t0)
 

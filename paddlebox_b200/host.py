@@ -418,6 +418,15 @@ class NativeDataset:
         return u[:nu.value].copy(), f[:nf.value].copy(), sid.value
 
 
+def sort_unique_u64(keys: np.ndarray) -> np.ndarray:
+    """Sorted unique keys (parallel sample sort on the host pool; ``np.unique`` for large key sets)."""
+    k = np.array(keys, dtype=np.uint64, copy=True).reshape(-1)
+    fn = N.host().pbh_sort_unique_u64
+    fn.restype = C.c_int64
+    n = fn(_u64p(k), C.c_int64(k.size))
+    return k[:n]
+
+
 def compute_batch_ranges(ins_num: int, batch_size: int, nworkers: int):
     lib = N.host()
     lib.pbh_compute_batch_ranges.restype = C.c_int64
