@@ -78,4 +78,32 @@ int64_t pbh_sort_unique_u64(uint64_t* keys, int64_t n) {
   return dst[B];
 }
 
+// Groups keys by owning rank, owner = (mix64(key) >> 40) % nranks (pbx_owner_of, csrc/cuda/common.cuh):
+// out[0, n) holds rank 0's keys, then rank 1's, ...; counts[r] = how many rank r owns.  Order inside a
+// rank follows the input order.
+int pbh_partition_by_owner(const uint64_t* keys, int64_t n, int nranks, uint64_t* out, int64_t* counts) {
+  using namespace pbh;
+  PBH_REQUIRE(nranks >= 1 && nranks <= 65536, "nranks %d out of range", nranks);
+  ThreadPool* pool = sort_pool();
+  const int W = pool->size();
+  auto owner = [nranks](uint64_t k) { return (int)((mix64(k) >> 40) % (uint64_t)nranks); };
+  std::vector<std::vector<int64_t>> cnt(W, std::vector<int64_t>(nranks, 0));
+  pool->parallel_range((size_t)n, [&](size_t b, size_t e, int w) {
+    auto& c = cnt[w];
+    for (size_t i = b; i < e; ++i) ++c[owner(keys[i])];
+  });
+  std::vector<std::vector<int64_t>> at(W, std::vector<int64_t>(nranks, 0));
+  int64_t t = 0;
+  for (int r = 0; r < nranks; ++r) {
+    int64_t first = t;
+    for (int w = 0; w < W; ++w) { at[w][r] = t; t += cnt[w][r]; }
+    counts[r] = t - first;
+  }
+  pool->parallel_range((size_t)n, [&](size_t b, size_t e, int w) {
+    auto& a = at[w];
+    for (size_t i = b; i < e; ++i) out[a[owner(keys[i])]++] = keys[i];
+  });
+  return 0;
+}
+
 }  // extern "C"

@@ -91,6 +91,9 @@ int64_t pbh_table_keys(void* t, uint64_t* out, int64_t max_n);
  * fleet/ps_gpu_wrapper.cc:114-335); returns the unique count */
 int64_t pbh_sort_unique_u64(uint64_t* keys, int64_t n);
 
+/* keys grouped by owning rank (owner = pbx_owner_of): out = rank 0's keys, rank 1's, ...; counts[r] */
+int pbh_partition_by_owner(const uint64_t* keys, int64_t n, int nranks, uint64_t* out, int64_t* counts);
+
 /* InputTable key index: string key -> row offset, 0 = miss (InputTable::AddIndexData / GetIndexOffset,
  * fleet/box_wrapper.h:124-197).  Attached to a dataset, a parser plugin that also exports
  *   void pbx_set_offset_func(uint64_t (*fn)(void* user, const char* key, size_t len), void* user)

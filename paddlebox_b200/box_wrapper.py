@@ -205,13 +205,10 @@ class BoxWrapper:
         keys = sort_unique_u64(np.concatenate(self._feed_keys)) if self._feed_keys else np.zeros(0, np.uint64)
         self._feed_keys = []
         if self.world_size > 1:
-            import torch.distributed as dist
-            own = owner_of(keys, self.world_size)
-            # control-plane exchange of key lists (sizes first, then padded payloads)
-            parts = [keys[own == r] for r in range(self.world_size)]
-            gathered = [None] * self.world_size
-            dist.all_gather_object(gathered, [p.tobytes() for p in parts], group=self.group)
-            mine = [np.frombuffer(g[self.rank], dtype=np.uint64) for g in gathered]
+            from .host import partition_by_owner
+            from .parallel.cluster import Cluster
+            # every key goes to the rank that owns it: one native partition, one all-to-all of raw keys
+            mine = Cluster(self.group).all_to_all_arrays(partition_by_owner(keys, self.world_size))
             keys = sort_unique_u64(np.concatenate(mine)) if mine else np.zeros(0, np.uint64)
         self._pass_keys = keys
         self.timers.add("feed_pass", time.time() - t0)

@@ -427,6 +427,17 @@ def sort_unique_u64(keys: np.ndarray) -> np.ndarray:
     return k[:n]
 
 
+def partition_by_owner(keys: np.ndarray, nranks: int) -> list:
+    """``[keys owned by rank 0, by rank 1, ...]`` (views of one array; owner = ``pbx_owner_of``)."""
+    k = np.ascontiguousarray(keys, dtype=np.uint64).reshape(-1)
+    out = np.empty_like(k)
+    counts = np.zeros(nranks, dtype=np.int64)
+    N.hcheck(N.host().pbh_partition_by_owner(_u64p(k), C.c_int64(k.size), nranks, _u64p(out),
+                                             counts.ctypes.data_as(C.POINTER(C.c_int64))))
+    ends = np.cumsum(counts)
+    return [out[e - c:e] for c, e in zip(counts.tolist(), ends.tolist())]
+
+
 def compute_batch_ranges(ins_num: int, batch_size: int, nworkers: int):
     lib = N.host()
     lib.pbh_compute_batch_ranges.restype = C.c_int64

@@ -77,6 +77,30 @@ class Cluster:
         dist.all_reduce(t, group=self.group)
         return t.cpu().numpy()
 
+    def all_to_all_arrays(self, parts: Sequence[np.ndarray]) -> list:
+        """``parts[d]`` (1-D array, same dtype on every rank) goes to rank d; returns what every rank
+        sent here, by source rank.  One size exchange + one ``all_to_all`` of the raw data — no pickling."""
+        if self.size() == 1:
+            return [np.asarray(parts[0])]
+        dev = self._staging_device()
+        dtype = np.asarray(parts[0]).dtype
+        send_counts = torch.tensor([int(np.asarray(p).size) for p in parts], dtype=torch.int64, device=dev)
+        recv_counts = torch.empty_like(send_counts)
+        dist.all_to_all_single(recv_counts, send_counts, group=self.group)
+        sc, rc = send_counts.tolist(), recv_counts.tolist()
+        flat = np.ascontiguousarray(np.concatenate([np.asarray(p).reshape(-1) for p in parts])).view(np.uint8)
+        send = torch.from_numpy(flat.copy()).to(dev)
+        item = dtype.itemsize
+        recv = torch.empty(sum(rc) * item, dtype=torch.uint8, device=dev)
+        dist.all_to_all_single(recv, send, output_split_sizes=[c * item for c in rc],
+                               input_split_sizes=[c * item for c in sc], group=self.group)
+        got = recv.cpu().numpy().view(dtype)
+        out, off = [], 0
+        for c in rc:
+            out.append(got[off:off + c])
+            off += c
+        return out
+
     def allgather_object(self, obj) -> list:
         if self.size() == 1:
             return [obj]
