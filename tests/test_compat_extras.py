@@ -408,3 +408,24 @@ def test_pipeline_by_section_matches_plain_training():
     assert abs(loss - float(ref_loss.detach())) < 1e-5
     for p, q in zip(pipe.parameters(), ref.parameters()):
         assert torch.allclose(p.grad, q.grad, atol=1e-6)
+
+
+def test_examples_run_on_cpu(tmp_path):
+    import subprocess
+    import sys
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")}
+    r = subprocess.run([sys.executable, os.path.join(root, "examples", "train_ctr.py"), "--cpu", "--passes", "4",
+                        "--lines", "512", "--out", str(tmp_path)], capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    lines = [ln for ln in r.stdout.splitlines() if ln.startswith("pass ")]
+    assert len(lines) == 4 and "day end" in r.stdout
+    aucs = [float(ln.split("auc ")[1].split()[0]) for ln in lines]
+    assert aucs[-1] > aucs[0] and aucs[-1] > 0.58, aucs
+    assert os.path.isdir(tmp_path / "batch_model") and os.path.isdir(tmp_path / "xbox_base")
+    r = subprocess.run([sys.executable, os.path.join(root, "examples", "graph_skipgram.py"), "--cpu", "--epochs", "3"],
+                       capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    ls = [float(ln.rsplit(" ", 1)[1]) for ln in r.stdout.splitlines() if ln.startswith("epoch")]
+    assert len(ls) == 3 and ls[-1] < ls[0]
