@@ -102,6 +102,62 @@ def seqpool_cvm_fwd(x: torch.Tensor, lod: torch.Tensor, B: int, S: int, *, use_c
     return out
 
 
+def seqpool_plain(kw: dict) -> bool:
+    """True when the attributes need none of the per-bag special cases (filters, quantisation,
+    embedx concat, trade weights, per-slot thresholds): the vectorised CPU path applies."""
+    return (not kw.get("need_filter") and not kw.get("embed_threshold_filter") and not kw.get("quant_ratio")
+            and kw.get("embedx_concate_size", 1) == 1 and kw.get("slot_threshold") is None
+            and kw.get("trade_w") is None)
+
+
+def seqpool_cvm_fwd_vec(x: torch.Tensor, lod: torch.Tensor, B: int, S: int, *, use_cvm=True, cvm_offset=2,
+                        pad_value=0.0, clk_filter=False, variant=0, show_filter=False, **_) -> torch.Tensor:
+    """Vectorised ``seqpool_cvm_fwd`` for plain attributes (one index_add instead of a loop over bags):
+    the CPU execution path of the framework; the loop above stays the oracle."""
+    H = x.shape[1]
+    lens = (lod[1:] - lod[:-1]).long()
+    n = int(lod[-1])
+    bag = torch.repeat_interleave(torch.arange(S * B, device=x.device), lens, output_size=n)
+    pooled = torch.zeros(S * B, H, dtype=torch.float64, device=x.device).index_add_(0, bag, x[:n].double())
+    pooled = (pooled + pad_value).float()
+    if use_cvm:
+        res = pooled.clone()
+        if variant == 0:
+            res[:, 0] = torch.log(pooled[:, 0] + 1)
+            res[:, 1] = torch.log(pooled[:, 1] + 1) - torch.log(pooled[:, 0] + 1)
+            if clk_filter:
+                res = torch.cat([res[:, :1], res[:, 2:]], 1)
+        elif variant == 1:
+            res[:, 0] = torch.log(pooled[:, 0] + 1)
+            res[:, 1] = torch.log(pooled[:, 1] + 1)
+            res[:, 2] = torch.log(pooled[:, 2] + 1) - torch.log(pooled[:, 1] + 1)
+            if show_filter:
+                res = res[:, 1:]
+        else:
+            res[:, :cvm_offset] = torch.log(pooled[:, :cvm_offset] + 1)
+            if show_filter:
+                res = res[:, 1:]
+    else:
+        res = pooled[:, cvm_offset:]
+    Eo = res.shape[1]
+    return res.reshape(S, B, Eo).permute(1, 0, 2).reshape(B, S * Eo).contiguous()
+
+
+def seqpool_cvm_bwd_vec(dout: torch.Tensor, cvm: torch.Tensor, lod: torch.Tensor, B: int, S: int, hidden: int, *,
+                        use_cvm=True, cvm_offset=2, clk_filter=False, variant=0, show_filter=False, **_) -> torch.Tensor:
+    """Vectorised ``seqpool_cvm_bwd`` (embedx_concate_size 1)."""
+    lens = (lod[1:] - lod[:-1]).long()
+    n = int(lod[-1])
+    dim_off = (1 if (clk_filter if variant == 0 else show_filter) else 0) if use_cvm else cvm_offset
+    Eo = hidden - dim_off
+    bag = torch.repeat_interleave(torch.arange(S * B, device=dout.device), lens, output_size=n)
+    s_of, b_of = bag // B, bag % B
+    dx = torch.empty(n, hidden, dtype=torch.float32, device=dout.device)
+    dx[:, :cvm_offset] = cvm[b_of, :cvm_offset]
+    dx[:, cvm_offset:] = dout[:, :S * Eo].reshape(B, S, Eo)[b_of, s_of, cvm_offset - dim_off:]
+    return dx
+
+
 def seqpool_cvm_bwd(dout: torch.Tensor, cvm: torch.Tensor, lod: torch.Tensor, B: int, S: int, hidden: int, *,
                     use_cvm=True, cvm_offset=2, clk_filter=False, embedx_concate_size=1, variant=0,
                     show_filter=False) -> torch.Tensor:

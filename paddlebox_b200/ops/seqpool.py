@@ -94,7 +94,9 @@ def seqpool_cvm_forward(x: torch.Tensor, lod: torch.Tensor, B: int, S: int, attr
     Eo = attrs.out_width(hidden)
     if not x.is_cuda:
         rows = x[restore.long()] if restore is not None else x
-        return R.seqpool_cvm_fwd(rows[:, :hidden], lod, B, S, **attrs.ref_kwargs())
+        kw = attrs.ref_kwargs()
+        fwd = R.seqpool_cvm_fwd_vec if R.seqpool_plain(kw) else R.seqpool_cvm_fwd
+        return fwd(rows[:, :hidden], lod, B, S, **kw)
     if out is None:
         out = torch.empty(B, S * Eo, dtype=torch.float32, device=x.device)
     p = _params(attrs, B, S, hidden, x.stride(0), out.stride(0))
@@ -112,9 +114,10 @@ def seqpool_cvm_forward(x: torch.Tensor, lod: torch.Tensor, B: int, S: int, attr
 def seqpool_cvm_backward(dout: torch.Tensor, cvm: torch.Tensor, lod: torch.Tensor, B: int, S: int, n_keys: int,
                          attrs: SeqpoolAttrs, hidden: int) -> torch.Tensor:
     if not dout.is_cuda:
-        return R.seqpool_cvm_bwd(dout, cvm, lod, B, S, hidden, use_cvm=attrs.use_cvm, cvm_offset=attrs.cvm_offset,
-                                 clk_filter=attrs.clk_filter, embedx_concate_size=attrs.embedx_concate_size,
-                                 variant=attrs.variant, show_filter=attrs.show_filter)
+        bwd = R.seqpool_cvm_bwd_vec if attrs.embedx_concate_size == 1 else R.seqpool_cvm_bwd
+        return bwd(dout, cvm, lod, B, S, hidden, use_cvm=attrs.use_cvm, cvm_offset=attrs.cvm_offset,
+                   clk_filter=attrs.clk_filter, embedx_concate_size=attrs.embedx_concate_size,
+                   variant=attrs.variant, show_filter=attrs.show_filter)
     dout = dout.contiguous()
     dx = torch.empty(max(n_keys, 1), hidden, dtype=torch.float32, device=dout.device)
     p = _params(attrs, B, S, hidden, hidden, dout.stride(0))

@@ -357,3 +357,29 @@ def test_queue_dataset_streams_in_file_order(tmp_path):
     want = [float(line.split()[1]) for line in open(files[0])]
     assert labels.tolist() == want
     assert ds.unique_keys().size == 0            # a streaming dataset does not collect pass keys
+
+
+def test_vectorised_cpu_seqpool_matches_the_loop_oracle():
+    import torch
+    from paddlebox_b200.ops import reference as R
+    gen = torch.Generator().manual_seed(0)
+    B, S, H = 7, 5, 9
+    lens = torch.randint(0, 4, (S * B,), generator=gen)
+    lod = torch.zeros(S * B + 1, dtype=torch.int32)
+    lod[1:] = torch.cumsum(lens, 0)
+    x = torch.rand(int(lod[-1]), H, generator=gen) * 3
+    cvm = torch.rand(B, 4, generator=gen)
+    for kw in (dict(use_cvm=True, cvm_offset=2), dict(use_cvm=True, cvm_offset=2, clk_filter=True),
+               dict(use_cvm=False, cvm_offset=2), dict(use_cvm=True, cvm_offset=3, variant=1),
+               dict(use_cvm=True, cvm_offset=3, variant=1, show_filter=True), dict(use_cvm=True, cvm_offset=4, variant=2),
+               dict(use_cvm=False, cvm_offset=3, variant=1), dict(use_cvm=True, cvm_offset=2, pad_value=0.5)):
+        assert R.seqpool_plain(kw)
+        a = R.seqpool_cvm_fwd(x, lod, B, S, **kw)
+        b = R.seqpool_cvm_fwd_vec(x, lod, B, S, **kw)
+        assert a.shape == b.shape and torch.allclose(a, b, atol=1e-6), kw
+        dout = torch.rand(B, a.shape[1], generator=gen)
+        bkw = {k: v for k, v in kw.items() if k != "pad_value"}
+        da = R.seqpool_cvm_bwd(dout, cvm, lod, B, S, H, **bkw)
+        db = R.seqpool_cvm_bwd_vec(dout, cvm, lod, B, S, H, **bkw)
+        assert torch.equal(da, db), kw
+    assert not R.seqpool_plain(dict(need_filter=True)) and not R.seqpool_plain(dict(embedx_concate_size=2))
