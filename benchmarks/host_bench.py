@@ -82,6 +82,27 @@ def main():
     t0 = time.time()
     tab.push(keys, push)
     out["host_table_push_rows_per_s"] = round(keys.size / (time.time() - t0))
+    # end of a feed pass: sort + unique of the pass keys, and their partition by owning rank
+    from paddlebox_b200.host import partition_by_owner, sort_unique_u64
+    raw = np.random.default_rng(1).integers(1, 1 << 62, 20_000_000, dtype=np.uint64)
+    t0 = time.time()
+    uk = sort_unique_u64(raw)
+    out["sort_unique_keys_per_s"] = round(raw.size / (time.time() - t0))
+    t0 = time.time()
+    partition_by_owner(uk, 8)
+    out["partition_by_owner_keys_per_s"] = round(uk.size / (time.time() - t0))
+    # SSD tier: spill half of the table, then promote it back
+    import tempfile as _tf
+    with _tf.TemporaryDirectory() as ssd:
+        tab.ssd_open(ssd)
+        tab.save(os.path.join(ssd, "delta"), mode=1, clear_dirty=True)      # clean rows may spill
+        t0 = time.time()
+        n_sp = tab.spill(max_mem_rows=keys.size // 2)
+        out["ssd_spill_rows_per_s"] = round(n_sp / max(time.time() - t0, 1e-9))
+        t0 = time.time()
+        n_ld = tab.load_ssd2mem()
+        out["ssd_load_rows_per_s"] = round(n_ld / max(time.time() - t0, 1e-9))
+        tab.ssd_close(True)
     auc = HostAuc(1_000_000)
     p, y = np.random.rand(4_000_000).astype(np.float32), (np.random.rand(4_000_000) < 0.2).astype(np.float32)
     t0 = time.time()
