@@ -277,10 +277,39 @@ class HostTable {
     const size_t S = shards_.size();
     std::vector<int64_t> cnt(S, 0);
     auto work = [&](size_t si) {
-      std::vector<uint64_t> ks;
-      for (auto& kv : ssd_[si].index) ks.push_back(kv.first);
-      for (uint64_t k : ks) cnt[si] += promote(shards_[si], ssd_[si], k) != nullptr;
+      // one sequential read of the shard file in large blocks; a record is live when the index still
+      // points at its offset (superseded and promoted records are skipped)
       SsdShard& d = ssd_[si];
+      Shard& s = shards_[si];
+      const size_t rb = rec_bytes();
+      const size_t per_block = std::max<size_t>(1, (size_t)(8 << 20) / rb);
+      std::vector<char> buf(per_block * rb);
+      s.rows.reserve(s.rows.size() + d.index.size() * L.stride);
+      for (uint64_t off = 0; off < d.end && !d.index.empty();) {
+        size_t want = (size_t)std::min<uint64_t>(buf.size(), d.end - off);
+        ssize_t got = pread(d.fd, buf.data(), want, (off_t)off);
+        if (got <= 0) break;
+        size_t recs = (size_t)got / rb;
+        if (recs == 0) break;
+        for (size_t r = 0; r < recs; ++r) {
+          uint64_t key;
+          memcpy(&key, buf.data() + r * rb, 8);
+          auto it = d.index.find(key);
+          if (it == d.index.end() || it->second != off + r * rb) continue;
+          d.index.erase(it);
+          uint32_t idx = (uint32_t)s.keys.size();
+          s.index.emplace(key, idx);
+          s.keys.push_back(key);
+          s.dirty.push_back(0);
+          const float* row = (const float*)(buf.data() + r * rb + 8);
+          s.rows.insert(s.rows.end(), row, row + L.stride);
+          ++cnt[si];
+        }
+        off += recs * rb;
+      }
+      std::vector<uint64_t> ks;                       // anything a short read left behind
+      for (auto& kv : d.index) ks.push_back(kv.first);
+      for (uint64_t k : ks) cnt[si] += promote(s, d, k) != nullptr;
       if (d.index.empty() && d.fd >= 0 && ftruncate(d.fd, 0) == 0) { d.end = 0; d.dead = 0; }
     };
     if (pool) pool->parallel_range(S, [&](size_t b, size_t e, int) { for (size_t i = b; i < e; ++i) work(i); });
