@@ -30,7 +30,62 @@ class PSGPUWrapper(BoxWrapper):
         self.slot_vector = list(slots)
 
     def set_slot_dim_vector(self, dims) -> None:
+        """Per-slot embedx widths (dynamic-mf mode).  With more than one distinct width, build a
+        ``multi_dim.MultiDimBox(self.slot_dim_vector)`` — one table per width."""
         self.slot_dim_vector = list(dims)
+
+    def set_slot_offset_vector(self, offsets) -> None:
+        self.slot_offset_vector = list(offsets)
+
+    def set_dataset(self, dataset) -> None:
+        self.dataset = dataset
+
+    def init(self, *a, **kw) -> None:
+        """``PSGPUWrapper::init``: nothing to pre-create here (tables are built by ``init_gpu_ps``)."""
+
+    def init_gpu_ps(self, gpus=None, conf: dict | None = None, **kw) -> None:
+        """``InitializeGPU(dev_ids)``: this process drives the current device only (one process per GPU)."""
+        if not self._initialized:
+            self.initialize_gpu_and_load_model(conf or {}, **kw)
+
+    # ---- AFS / HDFS client names of ps_gpu_wrapper_py.cc (delegating to BoxFileMgr) -----------------
+    def _fm(self):
+        fm = getattr(self, "file_mgr", None)
+        if fm is None:
+            from .side_tables import BoxFileMgr
+            fm = self.file_mgr = BoxFileMgr()
+        return fm
+
+    def list(self, path: str) -> list:
+        return self._fm().list_dir(path)
+
+    def exist(self, path: str) -> bool:
+        return self._fm().exists(path)
+
+    def mkdir(self, path: str) -> bool:
+        return self._fm().makedir(path)
+
+    def remove(self, path: str) -> bool:
+        return self._fm().remove(path)
+
+    def mv(self, src: str, dst: str) -> bool:
+        return self._fm().rename(src, dst)
+
+    def touchz(self, path: str) -> bool:
+        return self._fm().touch(path)
+
+    def upload(self, local: str, remote: str) -> bool:
+        return self._fm().upload(local, remote)
+
+    def download(self, local: str, remote: str) -> bool:
+        return self._fm().download(remote, local)
+
+    def cat(self, path: str) -> str:
+        fm = self._fm()
+        if fm._remote(path):
+            return fm._run("-cat", path).stdout
+        with open(path) as f:
+            return f.read()
 
     # SetSparseSGD / SetEmbedxSGD (fleet/ps_gpu_wrapper.cu:139-187): the two halves of the sparse
     # optimizer configuration, applied to the host tier and the HBM shard

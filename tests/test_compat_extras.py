@@ -429,3 +429,27 @@ def test_examples_run_on_cpu(tmp_path):
     assert r.returncode == 0, r.stdout + r.stderr
     ls = [float(ln.rsplit(" ", 1)[1]) for ln in r.stdout.splitlines() if ln.startswith("epoch")]
     assert len(ls) == 3 and ls[-1] < ls[0]
+
+
+def test_psgpu_wrapper_pybind_names(tmp_path):
+    import torch
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    from paddlebox_b200.ps_gpu import PSGPUWrapper
+    BoxWrapper.reset_instance()
+    ps = PSGPUWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=0, world_size=1)
+    try:
+        assert isinstance(ps, PSGPUWrapper)
+        ps.init()
+        ps.init_gpu_ps([0], {"mf_create_thresholds": 0.0})
+        ps.set_slot_vector([1, 2, 3]); ps.set_slot_dim_vector([4, 4, 4]); ps.set_slot_offset_vector([0, 1, 2])
+        ps.set_sparse_sgd(learning_rate=0.2); ps.set_embedx_sgd(mf_learning_rate=0.3)
+        assert abs(ps.host_table.config.learning_rate - 0.2) < 1e-7 and abs(ps.host_table.config.mf_learning_rate - 0.3) < 1e-7
+        d = str(tmp_path / "x")
+        assert ps.mkdir(d) and ps.exist(d) and ps.touchz(d + "/a") and ps.list(d) == [d + "/a"]
+        assert ps.mv(d + "/a", d + "/b") and ps.cat(d + "/b") == "" and ps.upload(d + "/b", d + "/c")
+        assert ps.download(d + "/e", d + "/c") and ps.remove(d + "/b") and sorted(ps.list(d)) == [d + "/c", d + "/e"]
+        ps.build_task(torch.arange(1, 20))
+        assert ps.host_table.size() == 20
+        ps.end_pass()
+    finally:
+        BoxWrapper.reset_instance()
