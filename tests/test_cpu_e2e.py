@@ -133,3 +133,46 @@ def test_owner_hash_matches_device_definition():
         return k
     assert mix64_np(keys).tolist() == [mix(int(k)) for k in keys]
     assert owner_of(keys, 8).tolist() == [(mix(int(k)) >> 40) % 8 for k in keys]
+
+
+def test_serving_predictor_reproduces_training_predictions(tmp_path, box):
+    """xbox base + delta + dense persistables -> Predictor gives the trainer's own predictions."""
+    from paddlebox_b200.checkpoint import save_persistables
+    from paddlebox_b200.serving import Predictor
+    torch.manual_seed(0)
+    (tmp_path / "data").mkdir()
+    ds = _dataset(tmp_path / "data", n_sparse=4, n_dense=2, lines=128, files=1)
+    model = CtrDnn(num_slots=4, embedx_dim=8, dense_dim=2, hidden=(16,))
+    trainer = CTRTrainer(model, box)
+    ds.load_into_memory()
+    for p in range(2):
+        ds.begin_pass()
+        trainer.train_from_dataset(ds)
+        ds.end_pass()
+        if p == 0:
+            box.save_base(str(tmp_path / "batch"), str(tmp_path / "xbox_base"), "20240101")
+    box.save_delta(str(tmp_path / "xbox_delta"))
+    save_persistables(model, str(tmp_path / "dense"))
+    ds.begin_pass()
+    ds.prepare_train(1, 0, shuffle=False)
+    batches = list(ds.batches())
+    want = [trainer.infer_step(b)[1]["pred"].clone() for b in batches]
+    ds.end_pass()
+    n_feat = box.host_table.size()
+    BoxWrapper.reset_instance()
+    torch.manual_seed(5)                                   # different init: the weights must come from disk
+    pred = Predictor(CtrDnn(num_slots=4, embedx_dim=8, dense_dim=2, hidden=(16,)), str(tmp_path / "xbox_base"),
+                     [str(tmp_path / "xbox_delta")], dense_dir=str(tmp_path / "dense"), embedx_dim=8,
+                     device=torch.device("cpu"))
+    try:
+        assert pred.num_features == n_feat
+        for b, w in zip(batches, want):
+            assert torch.allclose(pred.predict(b), w, atol=1e-5)
+        rows_before = pred.box.host_table.fetch_rows(pred.box.host_table.keys(), create=False).copy()
+        unseen = batches[0]
+        unseen.keys = unseen.keys + 10_000_000              # unknown feasigns: zeros, and nothing is created
+        p = pred.predict(unseen)
+        assert torch.isfinite(p).all() and pred.num_features == n_feat
+        assert np.array_equal(pred.box.host_table.fetch_rows(pred.box.host_table.keys(), create=False), rows_before)
+    finally:
+        pred.close()
