@@ -237,6 +237,12 @@ def cpu_global_shuffle_and_cluster(rank, world):
     biggest = c.allreduce(int(n_after), OP_MAX)
     sums = c.allreduce_sum([float(rank + 1), 1.0])
     ranks = c.allgather_object(rank)
+    from paddlebox_b200 import fleet
+    fleet.init()
+    assert fleet.worker_index() == rank and fleet.worker_num() == world and fleet.is_first_worker() == (rank == 0)
+    shard = fleet.util.get_file_shard([f"f{i}" for i in range(5)])
+    assert shard == ([f"f{i}" for i in range(3)] if rank == 0 else ["f3", "f4"])
+    assert fleet.util.all_reduce(rank + 1, "max") == world and fleet.util.all_gather(rank) == list(range(world))
     c.barrier()
     return dict(before=n_before, after=n_after, total_before=total_before, total_after=total_after,
                 biggest=biggest, sums=sums.tolist(), ranks=ranks)
