@@ -138,6 +138,8 @@ int pbh_dataset_set_int(void* h, const char* key, int64_t v) {
   else if (k == "collect_keys") d->collect_keys = v != 0;
   else if (k == "compact_batches") d->compact_batches = (int)v;
   else if (k == "compact_limit_mb") d->compact_limit_mb = (int64_t)v;
+  else if (k == "parser_file_mode") d->parser_file_mode = v != 0;
+  else if (k == "parser_file_mode") d->parser_file_mode = v != 0;
   else if (k == "rank") d->rank = (int)v;
   else if (k == "world") d->world = (int)v;
   else { pbh::set_error("unknown dataset option %s", key); return -1; }

@@ -225,7 +225,9 @@ int Dataset::bind_plugin() {
     plugin_handle_ = dlopen(parser_plugin.c_str(), RTLD_NOW | RTLD_LOCAL);
     PBH_REQUIRE(plugin_handle_ != nullptr, "cannot dlopen parser plugin %s: %s", parser_plugin.c_str(), dlerror());
     plugin_fn_ = dlsym(plugin_handle_, "pbx_parse_line");
-    PBH_REQUIRE(plugin_fn_ != nullptr, "parser plugin %s lacks symbol pbx_parse_line", parser_plugin.c_str());
+    plugin_file_fn_ = dlsym(plugin_handle_, "pbx_parse_file");
+    PBH_REQUIRE(plugin_fn_ != nullptr || plugin_file_fn_ != nullptr,
+                "parser plugin %s exports neither pbx_parse_line nor pbx_parse_file", parser_plugin.c_str());
   }
   if (plugin_handle_ && input_index) {
     // optional: void pbx_set_offset_func(uint64_t (*fn)(void* user, const char* key, size_t len), void* user)
@@ -302,6 +304,7 @@ struct PluginCtx {
   std::string ins_id;
   uint64_t search_id = 0;
   uint32_t rank = 0, cmatch = 0;
+  void* owner = nullptr;         // whole-file mode: the FileCtx this belongs to
 };
 typedef int (*plugin_fn_t)(const char*, size_t, void*, void (*)(void*, int, const uint64_t*, size_t),
                            void (*)(void*, int, const float*, size_t),
@@ -320,10 +323,10 @@ static void plug_emit_meta(void* c, const char* ins, uint64_t sid, uint32_t rank
   ctx->search_id = sid; ctx->rank = rank; ctx->cmatch = cmatch;
 }
 
-bool Dataset::parse_line(const char* line, size_t len, SlotRecord* rec) const {
-  const char* p = line;
-  const char* e = line + len;
-  while (e > p && (e[-1] == '\n' || e[-1] == '\r')) --e;
+// one record from what a parser plugin emitted (zero feasigns / tiny floats of sparse slots dropped like
+// the text parser does)
+bool Dataset::record_from_plugin(void* vctx, SlotRecord* rec) const {
+  PluginCtx& ctx = *(PluginCtx*)vctx;
   rec->reset();
   rec->u64_offs.assign(n_used_u64_ + 1, 0);
   rec->f_offs.assign(n_used_f_ + 1, 0);
@@ -333,25 +336,48 @@ bool Dataset::parse_line(const char* line, size_t len, SlotRecord* rec) const {
   f32s.resize(n_used_f_);
   for (auto& v : u64s) v.clear();
   for (auto& v : f32s) v.clear();
+  rec->ins_id = ctx.ins_id; rec->search_id = ctx.search_id; rec->rank = ctx.rank; rec->cmatch = ctx.cmatch;
+  for (size_t s = 0; s < slots.size(); ++s) {
+    if (!slots[s].is_used) continue;
+    if (slots[s].type == 0) {
+      auto& dst = u64s[slot_to_sparse_[s]];
+      for (uint64_t v : ctx.u64[s]) if (v != 0 || slots[s].is_dense) dst.push_back(v);
+    } else {
+      auto& dst = f32s[float_idx_[s]];
+      for (float v : ctx.f32[s]) if (slots[s].is_dense || std::fabs(v) >= 1e-6f) dst.push_back(v);
+    }
+  }
+  size_t total_u64 = 0;
+  for (int s = 0; s < n_used_u64_; ++s) {
+    rec->u64_vals.insert(rec->u64_vals.end(), u64s[s].begin(), u64s[s].end());
+    total_u64 += u64s[s].size();
+    rec->u64_offs[s + 1] = (uint32_t)total_u64;
+  }
+  size_t total_f = 0;
+  for (int s = 0; s < n_used_f_; ++s) {
+    rec->f_vals.insert(rec->f_vals.end(), f32s[s].begin(), f32s[s].end());
+    total_f += f32s[s].size();
+    rec->f_offs[s + 1] = (uint32_t)total_f;
+  }
+  return !(n_used_u64_ > 0 && total_u64 == 0);          // no feasign at all (data_feed.cc:4133)
+}
 
+bool Dataset::parse_line(const char* line, size_t len, SlotRecord* rec) const {
+  const char* p = line;
+  const char* e = line + len;
+  while (e > p && (e[-1] == '\n' || e[-1] == '\r')) --e;
   if (plugin_fn_) {
     PluginCtx ctx;
     ctx.u64.resize(slots.size());
     ctx.f32.resize(slots.size());
     if (((plugin_fn_t)plugin_fn_)(line, (size_t)(e - line), &ctx, plug_emit_u64, plug_emit_f32, plug_emit_meta) != 0)
       return false;
-    rec->ins_id = ctx.ins_id; rec->search_id = ctx.search_id; rec->rank = ctx.rank; rec->cmatch = ctx.cmatch;
-    for (size_t s = 0; s < slots.size(); ++s) {
-      if (!slots[s].is_used) continue;
-      if (slots[s].type == 0) {
-        auto& dst = u64s[slot_to_sparse_[s]];
-        for (uint64_t v : ctx.u64[s]) if (v != 0 || slots[s].is_dense) dst.push_back(v);
-      } else {
-        auto& dst = f32s[float_idx_[s]];
-        for (float v : ctx.f32[s]) if (slots[s].is_dense || std::fabs(v) >= 1e-6f) dst.push_back(v);
-      }
-    }
-  } else {
+    return record_from_plugin(&ctx, rec);
+  }
+  rec->reset();
+  rec->u64_offs.assign(n_used_u64_ + 1, 0);
+  rec->f_offs.assign(n_used_f_ + 1, 0);
+  {
     const char* tb; size_t tl; uint64_t n;
     if (parse_ins_id) {
       if (!read_u64(p, e, &n) || n != 1 || !read_token(p, e, &tb, &tl)) return false;
@@ -394,23 +420,73 @@ bool Dataset::parse_line(const char* line, size_t len, SlotRecord* rec) const {
     if (n_used_u64_ > 0 && rec->u64_vals.empty()) return false;  // no feasign at all (data_feed.cc:4133)
     return true;
   }
-  size_t total_u64 = 0;
-  for (int s = 0; s < n_used_u64_; ++s) {
-    rec->u64_vals.insert(rec->u64_vals.end(), u64s[s].begin(), u64s[s].end());
-    total_u64 += u64s[s].size();
-    rec->u64_offs[s + 1] = (uint32_t)total_u64;
-  }
-  size_t total_f = 0;
-  for (int s = 0; s < n_used_f_; ++s) {
-    rec->f_vals.insert(rec->f_vals.end(), f32s[s].begin(), f32s[s].end());
-    total_f += f32s[s].size();
-    rec->f_offs[s + 1] = (uint32_t)total_f;
-  }
-  if (n_used_u64_ > 0 && total_u64 == 0) return false;  // no feasign at all (data_feed.cc:4133)
-  return true;
+}
+
+// ---- whole-file parser plugins (FLAGS_enable_ins_parser_file: ISlotParser::ParseFileInstance,
+// data_feed.cc:3795-3883).  Optional plugin export:
+//   int pbx_parse_file(const char* path, void* ctx,
+//                      void (*begin_record)(void*), emit_u64, emit_f32, emit_meta,   // as in pbx_parse_line
+//                      int (*end_record)(void*));      // returns 0 when the record was kept
+// The plugin opens and reads the file itself (any container format) and reports record after record.
+struct FileCtx {
+  PluginCtx cur;                 // the plugin's ctx pointer is &cur; cur.owner leads back here
+  const Dataset* ds = nullptr;
+  std::function<void(SlotRecord*)> sink;
+  std::function<SlotRecord*()> alloc;
+  std::function<void(SlotRecord*)> discard;
+  int64_t good = 0, bad = 0;
+};
+static void file_begin_record(void* c) {
+  auto* f = (FileCtx*)((PluginCtx*)c)->owner;
+  for (auto& v : f->cur.u64) v.clear();
+  for (auto& v : f->cur.f32) v.clear();
+  f->cur.ins_id.clear();
+  f->cur.search_id = 0; f->cur.rank = 0; f->cur.cmatch = 0;
+}
+static int file_end_record(void* c) {
+  auto* f = (FileCtx*)((PluginCtx*)c)->owner;
+  SlotRecord* rec = f->alloc();
+  if (!f->ds->record_from_plugin(&f->cur, rec)) { f->discard(rec); ++f->bad; return 1; }
+  f->sink(rec);
+  ++f->good;
+  return 0;
+}
+typedef int (*plugin_file_fn_t)(const char*, void*, void (*)(void*), void (*)(void*, int, const uint64_t*, size_t),
+                                void (*)(void*, int, const float*, size_t),
+                                void (*)(void*, const char*, uint64_t, uint32_t, uint32_t), int (*)(void*));
+
+int Dataset::read_file_with_plugin(const std::string& path) {
+  FileCtx fc;
+  fc.ds = this;
+  fc.cur.owner = &fc;
+  fc.cur.u64.resize(slots.size());
+  fc.cur.f32.resize(slots.size());
+  std::vector<SlotRecord*> block;
+  block.reserve(4096);
+  int64_t feas = 0;
+  fc.alloc = [this] { return pool_.get(); };
+  fc.discard = [this](SlotRecord* r) { std::vector<SlotRecord*> one{r}; pool_.put(one); };
+  fc.sink = [&](SlotRecord* rec) {
+    feas += (int64_t)rec->u64_vals.size();
+    block.push_back(rec);
+    if (block.size() >= 4096) {
+      std::vector<SlotRecord*> out;
+      out.swap(block);
+      chan_.put(std::move(out));
+      block.reserve(4096);
+    }
+  };
+  int rc = ((plugin_file_fn_t)plugin_file_fn_)(path.c_str(), &fc.cur, file_begin_record, plug_emit_u64, plug_emit_f32,
+                                               plug_emit_meta, file_end_record);
+  if (!block.empty()) chan_.put(std::move(block));
+  lines_read_ += fc.good + fc.bad;
+  lines_bad_ += fc.bad;
+  total_feasigns_ += feas;
+  return rc == 0 ? 0 : -1;
 }
 
 int Dataset::read_file(const std::string& path) {
+  if (parser_file_mode && plugin_file_fn_) return read_file_with_plugin(path);
   FILE* fp = nullptr;
   bool piped = false;
   if (pipe_command.empty() || pipe_command == "cat") {
@@ -985,11 +1061,12 @@ int Dataset::load_archive(const std::string& path) {
 }
 
 std::string Dataset::last_stats() const {
-  std::ostringstream os;
-  os << "records=" << records_.size() << " lines=" << lines_read_.load() << " bad_lines=" << lines_bad_.load()
-     << " feasigns=" << total_feasigns_.load() << " unique_keys=" << unique_keys_.size()
-     << " read_s=" << load_seconds_ << " key_merge_s=" << merge_seconds_ << " pool_idle=" << 0;
-  return os.str();
+  char buf[512];
+  snprintf(buf, sizeof(buf),
+           "records=%zu lines=%lld bad_lines=%lld feasigns=%lld unique_keys=%zu read_s=%.6g key_merge_s=%.6g pool_idle=0",
+           records_.size(), (long long)lines_read_.load(), (long long)lines_bad_.load(),
+           (long long)total_feasigns_.load(), unique_keys_.size(), (double)load_seconds_, (double)merge_seconds_);
+  return std::string(buf);
 }
 
 }  // namespace pbh

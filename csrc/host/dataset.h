@@ -181,12 +181,16 @@ class Dataset {
   double load_seconds_ = 0, merge_seconds_ = 0;
   void* plugin_handle_ = nullptr;
   void* plugin_fn_ = nullptr;
+  void* plugin_file_fn_ = nullptr;
   int bind_plugin();
+  int read_file_with_plugin(const std::string& path);
 
  public:
   // string key -> row offset index of the InputTable (pbh_input_index_*); when set, a parser plugin
   // that exports pbx_set_offset_func receives the lookup callback (GetOffsetFunc, data_feed.cc:4487)
   void* input_index = nullptr;
+  bool parser_file_mode = false;   // the plugin's pbx_parse_file reads whole files (FLAGS_enable_ins_parser_file)
+  bool record_from_plugin(void* plugin_ctx, SlotRecord* rec) const;
 
  private:
 };

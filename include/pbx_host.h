@@ -63,7 +63,13 @@ int64_t pbh_compute_batch_ranges(int64_t ins_num, int batch_size, int nworkers, 
  *                      void (*emit_f32)(void*, int slot, const float*, size_t),
  *                      void (*emit_meta)(void*, const char* ins_id, uint64_t search_id,
  *                                        uint32_t rank, uint32_t cmatch));
- * and returns 0 for a good line. */
+ * and returns 0 for a good line.  Whole-file mode (FLAGS_enable_ins_parser_file; ParseFileInstance,
+ * data_feed.cc:3795-3883): the plugin may instead / also export
+ *   int pbx_parse_file(const char* path, void* ctx, void (*begin_record)(void*),
+ *                      emit_u64, emit_f32, emit_meta,           // as above
+ *                      int (*end_record)(void*));               // 0 = record kept
+ * and reads the file itself (any container format), bracketing every record with begin / end.
+ * Dataset option "parser_file_mode" = 1 selects it. */
 
 /* ---- host-memory table tier + CPU pull/push + checkpoints (csrc/host/host_table.cc) ----
  * reference: libbox_ps memory tier, pscore MemorySparseTable::Save

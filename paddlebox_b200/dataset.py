@@ -121,6 +121,8 @@ class DatasetBase:
         if pipe_command.endswith(".so"):
             self._native.set("parser_plugin", pipe_command)
             self._native.set("pipe_command", "cat")
+            # FLAGS_enable_ins_parser_file: the plugin's pbx_parse_file reads whole files
+            self._native.set("parser_file_mode", int(FLAGS.enable_ins_parser_file))
         else:
             self._native.set("pipe_command", pipe_command)
 

@@ -177,6 +177,54 @@ extern "C" int pbx_parse_line(const char* line, size_t len, void* ctx,
     assert d.num_records() == 2 and set(d.unique_keys().tolist()) == {0, 5, 6, 7, 8}
 
 
+def test_parser_plugin_whole_file_mode(tmp_path):
+    """pbx_parse_file: the plugin reads a binary container itself and reports record after record
+    (FLAGS_enable_ins_parser_file)."""
+    import struct
+    import subprocess
+    src = tmp_path / "plugf.cc"
+    src.write_text(r'''
+#include <cstdint>
+#include <cstdio>
+#include <vector>
+// file = records of: float label, uint32 n, n x uint64 keys
+extern "C" int pbx_parse_file(const char* path, void* ctx, void (*begin_record)(void*),
+    void (*emit_u64)(void*, int, const uint64_t*, size_t), void (*emit_f32)(void*, int, const float*, size_t),
+    void (*emit_meta)(void*, const char*, uint64_t, uint32_t, uint32_t), int (*end_record)(void*)) {
+  FILE* fp = fopen(path, "rb");
+  if (!fp) return 1;
+  float label; uint32_t n; uint64_t sid = 0;
+  while (fread(&label, 4, 1, fp) == 1 && fread(&n, 4, 1, fp) == 1) {
+    std::vector<uint64_t> ks(n);
+    if (n && fread(ks.data(), 8, n, fp) != n) { fclose(fp); return 2; }
+    begin_record(ctx);
+    emit_f32(ctx, 0, &label, 1);
+    emit_u64(ctx, 1, ks.data(), ks.size());
+    emit_meta(ctx, "f", ++sid, 0, 0);
+    end_record(ctx);
+  }
+  fclose(fp);
+  return 0;
+}''')
+    so = tmp_path / "plugf.so"
+    subprocess.check_call(["g++", "-shared", "-fPIC", "-O1", "-o", str(so), str(src)])
+    recs = [(1.0, [5, 6, 7]), (0.0, [8]), (1.0, []), (0.0, [0, 9])]     # third has no feasign: rejected
+    for name in ("a.bin", "b.bin"):
+        with open(tmp_path / name, "wb") as f:
+            for label, ks in recs:
+                f.write(struct.pack("<fI", label, len(ks)) + struct.pack(f"<{len(ks)}Q", *ks))
+    from paddlebox_b200.dataset import dense_slot, sparse_slot
+    d = NativeDataset()
+    d.set("parser_plugin", str(so))
+    d.set("parser_file_mode", 1)
+    d.set_slots([dense_slot("label").desc(), sparse_slot("a").desc()])
+    d.set("thread_num", 2)
+    d.set_filelist([str(tmp_path / "a.bin"), str(tmp_path / "b.bin")])
+    d.load_into_memory()
+    assert d.num_records() == 6 and set(d.unique_keys().tolist()) == {0, 5, 6, 7, 8, 9}
+    assert "records=6" in d.stats() and "bad_lines=2" in d.stats()
+
+
 # ---------------------------------------------------------------- host table
 @pytest.mark.parametrize("opt", ["adagrad", "adam", "shared_adam"])
 def test_host_table_matches_python_oracle(opt):
