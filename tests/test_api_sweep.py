@@ -1,0 +1,221 @@
+"""Calls the public entry points that no other test reaches, with a semantic check where one is cheap:
+rarely-used API surface is where latent crashes hide (Dataset.stats() used to be one)."""
+import io
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from paddlebox_b200.box_wrapper import BoxWrapper
+from paddlebox_b200.dataset import DatasetFactory
+from tests.util_data import slot_vars, write_files
+
+
+@pytest.fixture
+def box():
+    BoxWrapper.reset_instance()
+    b = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=0, world_size=1)
+    b.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0})
+    yield b
+    BoxWrapper.reset_instance()
+
+
+def test_dataset_setters_disk_mode_and_sampling(tmp_path, box):
+    files = write_files(str(tmp_path), n_files=2, lines_per_file=200, n_sparse=3, n_dense=2, key_space=30)
+    ds = DatasetFactory().create_dataset("PadBoxSlotDataset")
+    ds.init(batch_size=16, thread_num=2, use_var=slot_vars(3, 2), pipe_command="cat")
+    for name, arg in (("set_parse_content", True), ("set_merge_by_sid", True), ("set_queue_num", 4),
+                      ("set_fleet_send_batch_size", 512), ("set_fleet_send_sleep_seconds", 1), ("set_pv_batch_size", 8),
+                      ("set_ads_offset", "ads"), ("set_rank_offset", "rank_offset"), ("set_shuffle_seed", 3),
+                      ("set_max_rank", 3), ("set_trainer_num", 1)):
+        getattr(ds, name)(arg)
+    ds.set_fea_eval(100, True)
+    ds.disable_polling(False)
+    ds.disable_shuffle(False)
+    assert ds.num_sparse_slots == 3 and ds.dense_dim == 3
+    ds.set_filelist(files)
+    ds.set_date("20240101")
+    # Bernoulli sampling keeps roughly the asked share of the lines
+    ds.set_sample_rate(0.5)
+    ds.read_ins_into_memory()
+    n_half = ds.get_memory_data_size()
+    assert 120 < n_half < 280 and ds.get_shuffle_data_size() == n_half == ds.get_pv_data_size()
+    ds.release_memory()
+    ds.set_sample_rate(1.0)
+    # disk mode: parse once into an archive, load the archive later
+    ds.set_archivefile(str(tmp_path / "pass.bin"))
+    ds.load_into_disk()
+    assert ds.get_memory_data_size() == 0 and os.path.getsize(tmp_path / "pass.bin") > 0
+    ds.wait_load_disk_done()
+    assert ds.get_memory_data_size() == 400
+    ds.dynamic_adjust_readers_num(2)
+    assert ds._prepared_workers == 2
+    ds.preload_into_memory()
+    ds.wait_feed_pass_done()
+    assert "records=" in ds.stats() and "lines=" in ds.stats()
+
+
+def test_box_wrapper_phase_metric_registry_and_merge(tmp_path, box):
+    box.init_metric("AucCalculator", "join", "label", "pred", metric_phase=1, bucket_size=1000)
+    box.init_metric("AucCalculator", "update", "label", "pred", metric_phase=0, bucket_size=1000)
+    box.init_metric("NanInfCalculator", "nan", "label", "pred", metric_phase=1, bucket_size=1000)
+    assert box.get_metric_name_list(1) == ["join", "nan"] and box.get_metric_name_list(0) == ["update"]
+    assert set(box.get_metric_name_list()) == {"join", "update", "nan"}
+    assert box.phase() == 1
+    box.add_metric_data({"pred": torch.tensor([0.2, float("nan"), float("inf"), 0.9]), "label": torch.tensor([0., 1., 0., 1.])})
+    box.flip_phase()
+    assert box.phase() == 0
+    box.add_metric_data({"pred": torch.tensor([0.3, 0.6]), "label": torch.tensor([0., 1.])})
+    assert box.get_metric_msg("update")[7] == 2 and box.get_metric_msg("join")[7] == 4
+    nan_msg = box.get_nan_inf_metric_msg("nan")
+    assert nan_msg[0] == 1 and nan_msg[1] == 1
+    box.set_phase(1)
+    # merge_model: rows of another checkpoint replace / extend the table
+    keys = np.arange(1, 11, dtype=np.uint64)
+    rows = box.host_table.fetch_rows(keys)
+    rows[:, 2] = 7.0
+    box.host_table.store_rows(keys, rows)
+    box.save_base(str(tmp_path / "m"))
+    rows[:, 2] = 1.0
+    box.host_table.store_rows(keys[:5], rows[:5])
+    more = np.arange(100, 103, dtype=np.uint64)
+    box.host_table.fetch_rows(more)
+    assert box.merge_model(str(tmp_path / "m")) == 10
+    assert np.all(box.host_table.fetch_rows(keys, create=False)[:, 2] == 7.0) and box.host_table.size() == 13
+    box.shrink_resource()
+
+
+def test_seqpool_layer_variants_against_the_loop_oracle():
+    from paddlebox_b200.ops import reference as R
+    from paddlebox_b200.ops import seqpool as SP
+    gen = torch.Generator().manual_seed(0)
+    B, S, H = 6, 3, 9
+    lens = torch.randint(1, 4, (S * B,), generator=gen)
+    lod = torch.zeros(S * B + 1, dtype=torch.int32)
+    lod[1:] = torch.cumsum(lens, 0)
+    n = int(lod[-1])
+    x = (torch.rand(n, H, generator=gen) * 3).requires_grad_(True)
+    cvm = torch.rand(B, 4, generator=gen)
+    cases = [(SP.fused_seqpool_cvm_with_conv, {}, dict(variant=1, cvm_offset=3)),
+             (SP.fused_seqpool_cvm_with_conv, dict(show_filter=True), dict(variant=1, cvm_offset=3, show_filter=True)),
+             (SP.fused_seqpool_cvm_with_credit, {}, dict(variant=2, cvm_offset=4))]
+    for fn, kw, ref_kw in cases:
+        y = fn(x, cvm, lod, B, S, **kw)
+        assert torch.allclose(y, R.seqpool_cvm_fwd(x.detach(), lod, B, S, **ref_kw), atol=1e-5)
+        y.sum().backward()
+        co = ref_kw["cvm_offset"]
+        b_of = torch.repeat_interleave(torch.arange(S * B), lens) % B
+        assert torch.allclose(x.grad[:, :co], cvm[b_of, :co]) and torch.all(x.grad[:, co:] == 1)
+        x.grad = None
+    thr = [0.0, 1e9, 0.5]                                           # slot 1 filters everything out
+    y = SP.fused_seqpool_cvm_with_diff_thres(x.detach(), cvm, lod, B, S, thr, use_cvm=False)
+    ref = R.seqpool_cvm_fwd(x.detach(), lod, B, S, use_cvm=False, need_filter=True, quant_ratio=128,
+                            slot_threshold=torch.tensor(thr))
+    assert torch.allclose(y, ref, atol=1e-5) and torch.all(y[:, (H - 2):2 * (H - 2)] == 0)
+    tw = torch.rand(n, generator=gen)
+    y = SP.fused_seqpool_cvm_tradew(x.detach(), cvm, lod, B, S, tw, use_cvm=False)
+    want = torch.zeros(S * B, H - 2).index_add_(0, torch.repeat_interleave(torch.arange(S * B), lens),
+                                                x.detach()[:, 2:] * tw[:, None])
+    assert torch.allclose(y, want.view(S, B, -1).permute(1, 0, 2).reshape(B, -1), atol=1e-5)
+    parts = SP.split_slots(y, S)
+    assert len(parts) == S and parts[1].shape == (B, H - 2)
+
+
+def test_extended_sparse_rank_attention2_seq_tensor_dedup(box):
+    from paddlebox_b200.ops import ctr_ops as CO
+    from paddlebox_b200.ops import reference as R
+    from paddlebox_b200.ops.pull_box_sparse import SlotBatch, pull_box_extended_sparse
+    # expand embedding = trailing embedx columns (dim 4 table: size 3 + 2, extend 2)
+    keys = torch.tensor([5, 6, 5, 7], dtype=torch.int64)
+    box.begin_feed_pass("20240101"); box.feed_pass(keys); box.end_feed_pass(); box.begin_pass()
+    hk = np.array([5, 6, 7], np.uint64)
+    rows = box.host_table.fetch_rows(hk)
+    rows[:, 3:7] = np.arange(12, dtype=np.float32).reshape(3, 4)
+    rows[:, box.host_table.layout.off_mf] = 4
+    box.host_table.store_rows(hk, rows)
+    batch = SlotBatch(keys, torch.arange(5, dtype=torch.int32), 4, 1)
+    emb, ext = pull_box_extended_sparse(batch, size=5, extend_size=2, box=box)
+    assert emb.shape == (4, 5) and ext.shape == (4, 2)
+    assert ext[0].tolist() == [2.0, 3.0] and ext[1].tolist() == [6.0, 7.0] and torch.equal(ext[0], ext[2])
+    with pytest.raises(ValueError):
+        pull_box_extended_sparse(batch, size=5, extend_size=3, box=box)
+    box.end_pass()
+    # rank_attention2 = rank_attention
+    gen = torch.Generator().manual_seed(1)
+    xr = torch.rand(6, 5, generator=gen)
+    ro = CO.build_rank_offset(torch.tensor([1, 1, 1, 2, 2, 3]), torch.tensor([1, 2, 3, 1, 2, 1]), 3)
+    P = torch.rand(9 * 5, 4, generator=gen)
+    assert torch.equal(CO.rank_attention2(xr, ro, P, 3), CO.rank_attention(xr, ro, P, 3))
+    # fused_seq_tensor shapes and mask
+    ins, bc, L, sn, d, an = 2, 3, 4, 3, 2, 1
+    xs = torch.rand(ins * bc, sn * L * d, generator=gen)
+    xs.view(ins, bc, sn, L, d)[0, 0, :, 2:] = 0                     # two padded time steps
+    ad = torch.rand(ins * bc, 2 * d, generator=gen)
+    din, mask, side, sess = CO.fused_seq_tensor(xs, ad, bc, L, sn, d, an)
+    assert din.shape == (ins, bc, L, 2 * an * d) and side.shape == (ins, bc, L, (sn - an) * d) and sess.shape == (ins, bc, L, an * d)
+    assert mask[0, 0].tolist() == [1, 1, 0, 0] and mask[1].min() == 1
+    # dedup contract
+    k = torch.tensor([9, 3, 9, 1, 3, 9])
+    merged, restore, sorted_idx, offset, cnts = R.dedup_keys_and_fillidx(k)
+    assert merged.tolist() == [1, 3, 9] and cnts.tolist() == [1, 2, 3] and offset.tolist() == [0, 1, 3]
+    assert torch.equal(merged[restore], k)
+    for u in range(3):
+        occ = sorted_idx[offset[u]:offset[u] + cnts[u]]
+        assert torch.all(k[occ] == merged[u])
+
+
+def test_data_generator_monitor_optimizer_fleet_and_predict_dataset(tmp_path, box, capsys):
+    from paddlebox_b200 import fleet
+    from paddlebox_b200.data_generator import MultiSlotDataGenerator
+    from paddlebox_b200.models.ctr import CtrDnn
+    from paddlebox_b200.optimizer import Adam, BoxPSOptimizer
+    from paddlebox_b200.utils import monitor
+
+    class Gen(MultiSlotDataGenerator):
+        def generate_sample(self, line):
+            def it():
+                for i in range(5):
+                    yield [("label", [float(i % 2)]), ("dense", [0.5, 0.25]), ("s0", [i + 1, i + 2]), ("s1", [7])]
+            return it
+
+    g = Gen()
+    g.set_batch(2)
+    g.run_from_memory()
+    text = capsys.readouterr().out
+    assert text.count("\n") == 5 and text.splitlines()[0] == "1 0.0 2 0.5 0.25 2 1 2 1 7"
+    out = io.StringIO()
+    g.run_from_iterable(["x"], out)
+    assert out.getvalue() == text
+    (tmp_path / "d.txt").write_text(text * 8)
+    monitor.stat_reset()
+    monitor.stat_add("STAT_x", 2); monitor.stat_add("STAT_x")
+    assert monitor.stat_get("STAT_x") == 3 and monitor.stat_all() == {"STAT_x": 3}
+    monitor.stat_reset("STAT_x")
+    assert monitor.stat_get("STAT_x", -1) == -1
+    # BoxPSOptimizer.build_trainer + one pass + serving-style predict_dataset
+    ds = DatasetFactory().create_dataset("InMemoryDataset")
+    ds.set_use_var(slot_vars(2, 2))
+    ds.set_batch_size(8)
+    ds.set_filelist([str(tmp_path / "d.txt")])
+    ds.load_into_memory()
+    assert ds.get_memory_data_size() == 40
+    box.begin_feed_pass("20240101"); box.feed_pass(ds.unique_keys()); box.end_feed_pass(); box.begin_pass()
+    torch.manual_seed(0)
+    model = CtrDnn(num_slots=2, embedx_dim=4, dense_dim=2, hidden=(8,))
+    tr = BoxPSOptimizer(Adam(1e-2), sync_steps=1).build_trainer(model, box)
+    assert tr.cfg.dense_lr == 1e-2 and model._param_need_sync
+    stats = tr.train_from_dataset(ds)
+    assert stats["instances"] == 40
+    from paddlebox_b200.serving import Predictor
+    pred = Predictor.__new__(Predictor)                  # reuse the live box: only the dataset loop is under test
+    pred.box, pred.model = box, model
+    ds.prepare_train(1, 0, shuffle=False)
+    p = pred.predict_dataset(ds)
+    assert p.shape == (40,) and np.all((p > 0) & (p < 1))
+    box.end_pass()
+    fleet.init()
+    fleet.init_worker(); fleet.init_server()
+    assert fleet.is_worker() and not fleet.is_server()
+    fleet.util.print_on_rank("hello", 0)
+    assert "hello" in capsys.readouterr().out
