@@ -41,6 +41,12 @@ class AsyncDenseTable {
   }
   int64_t updates() const { return updates_.load(); }
   float lr_scale = 1.f;
+  // per-parameter learning rates (lr_map of InitializeGPUAndLoadModel, boxps_worker.cc:199-207)
+  void set_lr_range(int64_t begin, int64_t end, float lr) {
+    std::lock_guard<std::mutex> g(mu_);
+    if (lr_vec_.empty()) lr_vec_.assign((size_t)n_, lr_);
+    for (int64_t i = std::max<int64_t>(0, begin); i < std::min(end, n_); ++i) lr_vec_[i] = lr;
+  }
 
  private:
   void loop() {
@@ -64,15 +70,17 @@ class AsyncDenseTable {
       const float b1 = 0.99f, b2 = 0.9999f, eps = 1e-8f;
       b1pow_ *= b1;
       b2pow_ *= b2;
-      const float lr = lr_ * lr_scale * std::sqrt(1.f - b2pow_) / (1.f - b1pow_);
+      const float corr = lr_scale * std::sqrt(1.f - b2pow_) / (1.f - b1pow_);
+      const float lr = lr_ * corr;
       {
         std::lock_guard<std::mutex> g(mu_);
+        const float* lrv = lr_vec_.empty() ? nullptr : lr_vec_.data();
         pool_.parallel_range((size_t)n_, [&](size_t b, size_t e, int) {
           for (size_t i = b; i < e; ++i) {
             float gi = acc[i] * inv;
             m_[i] = b1 * m_[i] + (1.f - b1) * gi;
             v_[i] = b2 * v_[i] + (1.f - b2) * gi * gi;
-            w_[i] -= lr * m_[i] / (std::sqrt(v_[i]) + eps);
+            w_[i] -= (lrv ? lrv[i] * corr : lr) * m_[i] / (std::sqrt(v_[i]) + eps);
           }
         });
       }
@@ -84,7 +92,7 @@ class AsyncDenseTable {
   float lr_;
   ThreadPool pool_;
   int merge_limit_;
-  std::vector<float> w_, m_, v_;
+  std::vector<float> w_, m_, v_, lr_vec_;
   Channel<std::vector<float>> queue_;
   std::thread worker_;
   std::mutex mu_;
@@ -255,6 +263,10 @@ int pbh_async_dense_destroy(void* h) { delete (AsyncDenseTable*)h; return 0; }
 int pbh_async_dense_set_params(void* h, const float* p) { ((AsyncDenseTable*)h)->set_params(p); return 0; }
 int pbh_async_dense_pull(void* h, float* out) { ((AsyncDenseTable*)h)->pull(out); return 0; }
 int pbh_async_dense_push(void* h, const float* g) { ((AsyncDenseTable*)h)->push(g); return 0; }
+int pbh_async_dense_set_lr_range(void* h, int64_t begin, int64_t end, float lr) {
+  ((AsyncDenseTable*)h)->set_lr_range(begin, end, lr);
+  return 0;
+}
 int pbh_async_dense_wait(void* h) { ((AsyncDenseTable*)h)->wait_idle(); return 0; }
 int64_t pbh_async_dense_updates(void* h) { return ((AsyncDenseTable*)h)->updates(); }
 

@@ -141,6 +141,7 @@ int pbh_async_dense_destroy(void* t);
 int pbh_async_dense_set_params(void* t, const float* p);
 int pbh_async_dense_pull(void* t, float* out);
 int pbh_async_dense_push(void* t, const float* g);
+int pbh_async_dense_set_lr_range(void* t, int64_t begin, int64_t end, float lr);   /* lr_map, boxps_worker.cc:199-207 */
 int pbh_async_dense_wait(void* t);
 int64_t pbh_async_dense_updates(void* t);
 

@@ -184,6 +184,18 @@ class BoxWrapper:
         (0 unless ``feature_type`` 3)."""
         return int(round(1.0 / self.pull_embedx_scale)) if self.feature_type == 3 and self.pull_embedx_scale > 0 else 0
 
+    def get_lr_map(self) -> dict:
+        """Per-parameter learning rates for the async dense table: an ``lr_map`` entry whose name contains
+        ``param`` covers ``<name>.w_0`` and ``<name>.b_0`` (box_wrapper.cc:1233-1240); other entries are
+        taken as full parameter names."""
+        out = {}
+        for name, lr in self.lr_map.items():
+            if "param" in name:
+                out[name + ".w_0"] = out[name + ".b_0"] = float(lr)
+            else:
+                out[name] = float(lr)
+        return out
+
     # ---- pass lifecycle ------------------------------------------------------------------
     def set_date(self, date: str) -> None:
         self._day_id = make_day_id(date) if not FLAGS.fix_dayid or self._day_id == 0 else self._day_id

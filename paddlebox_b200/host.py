@@ -262,6 +262,10 @@ class AsyncDenseTable:
         g = np.ascontiguousarray(grad.detach().cpu().numpy(), dtype=np.float32)
         N.hcheck(N.host().pbh_async_dense_push(self._h, _f32p(g)))
 
+    def set_lr_range(self, begin: int, end: int, lr: float):
+        """Learning rate of the flat range ``[begin, end)`` (one parameter tensor; ``lr_map``)."""
+        N.hcheck(N.host().pbh_async_dense_set_lr_range(self._h, C.c_int64(begin), C.c_int64(end), C.c_float(lr)))
+
     def wait(self):
         N.hcheck(N.host().pbh_async_dense_wait(self._h))
 

@@ -58,6 +58,15 @@ class CTRTrainer:
         self.store = DenseParamStore(model, self.rank, self.world, group, topo=topo)
         self.opt = DenseOptimizer(self.store, lr=self.cfg.dense_lr, kind=self.cfg.dense_optimizer)
         self.sync = DenseSync(self.store, self.opt, mode, self.cfg.sync_weight_step)
+        if mode == "async" and self.box.lr_map:
+            # per-parameter learning rates of the async dense table (boxps_worker.cc:199-207)
+            lrs = self.box.get_lr_map()
+            named = list(model.named_dense_params()) if hasattr(model, "named_dense_params") else \
+                list(model.named_parameters())
+            offs = {id(p): o for p, o in zip(self.store.params, self.store.offsets)}
+            for n, p in named:
+                if n in lrs and id(p) in offs:
+                    self.sync.async_table.set_lr_range(offs[id(p)], offs[id(p)] + p.numel(), lrs[n])
         if self.world > 1 and not self.cfg.is_test:
             self.sync.fold_into(getattr(self.box, "engine", None))
         if self.world > 1:

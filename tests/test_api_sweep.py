@@ -219,3 +219,38 @@ def test_data_generator_monitor_optimizer_fleet_and_predict_dataset(tmp_path, bo
     assert fleet.is_worker() and not fleet.is_server()
     fleet.util.print_on_rank("hello", 0)
     assert "hello" in capsys.readouterr().out
+
+
+def test_lr_map_sets_per_parameter_rates_of_the_async_dense_table():
+    import time
+    from paddlebox_b200.host import AsyncDenseTable
+    from paddlebox_b200.models.ctr import CtrDnn
+    from paddlebox_b200.trainer import CTRTrainer, TrainerConfig
+    t = AsyncDenseTable(8, lr=0.1, threads=2)
+    t.set_params(torch.zeros(8))
+    t.set_lr_range(4, 8, 0.0)                               # frozen half
+    t.push(torch.ones(8)); t.wait()
+    w = t.pull()
+    assert torch.all(w[:4] < 0) and torch.all(w[4:] == 0)
+    BoxWrapper.reset_instance()
+    box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=0, world_size=1)
+    try:
+        box.initialize_gpu_and_load_model({}, lr_map={"fc_param_0": 0.0, "other": 0.5})
+        m = CtrDnn(num_slots=2, embedx_dim=4, dense_dim=2, hidden=(8,))
+        names = [n for n, _ in m.named_dense_params()]
+        box.lr_map = {"fc_param": 0.25, names[0]: 0.0}
+        got = box.get_lr_map()
+        assert got["fc_param.w_0"] == 0.25 and got["fc_param.b_0"] == 0.25 and got[names[0]] == 0.0
+        tr = CTRTrainer(m, box, TrainerConfig(async_mode=True, dense_lr=0.05))
+        p0 = dict(m.named_dense_params())[names[0]]
+        others_before = tr.store.flat.clone()
+        tr.store.gflat.fill_(1.0)
+        tr.sync.after_backward()
+        tr.sync.finalize()
+        o = tr.store.offsets[[id(p) for p in tr.store.params].index(id(p0))]
+        assert torch.equal(tr.store.flat[o:o + p0.numel()], others_before[o:o + p0.numel()])      # lr 0: untouched
+        mask = torch.ones_like(tr.store.flat, dtype=torch.bool)
+        mask[o:o + p0.numel()] = False
+        assert (tr.store.flat[mask] != others_before[mask]).float().mean() > 0.5
+    finally:
+        BoxWrapper.reset_instance()
