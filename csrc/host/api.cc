@@ -167,6 +167,10 @@ int pbh_dataset_set_str(void* h, const char* key, const char* v) {
   else { pbh::set_error("unknown dataset option %s", key); return -1; }
   return 0;
 }
+int pbh_dataset_set_omit_slots(void* h, const int* slot_indices, int n) {
+  ((Dataset*)h)->omit_slots.assign(slot_indices, slot_indices + n);
+  return 0;
+}
 int pbh_dataset_set_input_index(void* h, void* index) {
   Dataset* d = (Dataset*)h;
   d->input_index = index;           // the plugin's offset callback is bound when loading starts

@@ -543,12 +543,23 @@ void Dataset::reader_loop(std::atomic<size_t>* next_file, std::atomic<int>* erro
   }
 }
 
+void Dataset::collect_record_keys(const SlotRecord* r) {
+  if (omit_slots.empty()) {
+    agent_.add_keys(r->u64_vals.data(), r->u64_vals.size());
+    return;
+  }
+  for (size_t p = 0; p + 1 < r->u64_offs.size() && p < sparse_idx_.size(); ++p) {
+    if (std::find(omit_slots.begin(), omit_slots.end(), sparse_idx_[p]) != omit_slots.end()) continue;
+    agent_.add_keys(r->u64_vals.data() + r->u64_offs[p], r->u64_offs[p + 1] - r->u64_offs[p]);
+  }
+}
+
 void Dataset::merge_loop() {
   std::vector<SlotRecord*> block;
   std::vector<SlotRecord*> mine;
   while (chan_.get(block)) {
     if (collect_keys)
-      for (SlotRecord* r : block) agent_.add_keys(r->u64_vals.data(), r->u64_vals.size());
+      for (SlotRecord* r : block) collect_record_keys(r);
     mine.insert(mine.end(), block.begin(), block.end());
     block.clear();
     if (mine.size() >= 65536) {
@@ -1041,7 +1052,7 @@ int Dataset::load_archive(const std::string& path) {
       r->f_vals.resize(cnt); if (cnt) memcpy(r->f_vals.data(), q, (size_t)cnt * 4); q += (size_t)cnt * 4;
       memcpy(&no, q, 2); q += 2;
       r->f_offs.resize(no); if (no) memcpy(r->f_offs.data(), q, (size_t)no * 4);
-      if (collect_keys) agent_.add_keys(r->u64_vals.data(), r->u64_vals.size());
+      if (collect_keys) collect_record_keys(r);
       local_feas += (int64_t)r->u64_vals.size();
       records_[first + i] = r;
     }

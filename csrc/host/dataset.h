@@ -189,6 +189,10 @@ class Dataset {
   // string key -> row offset index of the InputTable (pbh_input_index_*); when set, a parser plugin
   // that exports pbx_set_offset_func receives the lookup callback (GetOffsetFunc, data_feed.cc:4487)
   void* input_index = nullptr;
+  // slots (indices into `slots`) whose feasigns are NOT parameter-server keys: left out of the feed
+  // pass (slot_omit_in_feedpass, data_feed.cc:3119-3146)
+  std::vector<int> omit_slots;
+  void collect_record_keys(const SlotRecord* r);
   bool parser_file_mode = false;   // the plugin's pbx_parse_file reads whole files (FLAGS_enable_ins_parser_file)
   bool record_from_plugin(void* plugin_ctx, SlotRecord* rec) const;
 

@@ -111,6 +111,9 @@ uint64_t pbh_input_index_get(void* ix, const char* key, size_t len);
 uint64_t pbh_input_index_size(void* ix);
 uint64_t pbh_input_index_miss(void* ix);
 int pbh_dataset_set_input_index(void* ds, void* ix);
+/* slots (indices in set_slots order) whose feasigns are not PS keys: skipped by the key collection
+ * (slot_omit_in_feedpass of InitializeGPUAndLoadModel, data_feed.cc:3119-3146) */
+int pbh_dataset_set_omit_slots(void* ds, const int* slot_indices, int n);
 /* SSD tier (closed-library LoadSSD2Mem / CheckNeedLimitMem, fleet/box_wrapper.cc:1316-1324): cold rows
  * move to one append-only file per shard under `dir`; a lookup that misses host memory promotes the
  * row back.  spill: rows unseen for >= min_unseen_days (negative: ignore age), then — if

@@ -118,6 +118,7 @@ class BoxWrapper:
         self._in_pass = False
         self.timers = StageTimers()
         self.slot_vector: list = []
+        self.slot_omit_in_feedpass: set = set()
         self.lr_map: dict = {}
         self.host_mem_rows_limit = 0
         self.ssd_unseen_days = -1.0

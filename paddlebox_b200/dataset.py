@@ -540,9 +540,20 @@ class BoxPSDataset(InMemoryDataset):
         self.boxps.feed_pass(self._native.unique_keys())
         self.boxps.end_feed_pass()
 
+    def _apply_omitted_slots(self):
+        """Slots named in ``slot_omit_in_feedpass`` carry ids that are not embedding keys (e.g. input-table
+        offsets): their feasigns stay out of the feed pass (data_feed.cc:3119-3146)."""
+        omit = {str(x) for x in getattr(self.boxps, "slot_omit_in_feedpass", ())}
+        self._native.set_omit_slots([i for i, s in enumerate(self.all_slots) if s.name in omit])
+
     def load_into_memory(self):
+        self._apply_omitted_slots()
         super().load_into_memory()
         self._feed_keys()
+
+    def preload_into_memory(self, thread_num: int | None = None):
+        self._apply_omitted_slots()
+        super().preload_into_memory(thread_num)
 
     def wait_preload_done(self):
         super().wait_preload_done()

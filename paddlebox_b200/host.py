@@ -314,6 +314,10 @@ class NativeDataset:
         else:
             N.hcheck(lib.pbh_dataset_set_int(self._h, key.encode(), C.c_int64(int(value))))
 
+    def set_omit_slots(self, slot_indices: Sequence[int]):
+        arr = (C.c_int * len(slot_indices))(*slot_indices)
+        N.hcheck(N.host().pbh_dataset_set_omit_slots(self._h, arr, len(slot_indices)))
+
     def set_input_index(self, index_handle):
         """Attach an ``InputTable`` key index (parse-time ``GetOffsetFunc`` for parser plugins)."""
         N.hcheck(N.host().pbh_dataset_set_input_index(self._h, index_handle))

@@ -314,7 +314,7 @@ extern "C" int pbx_parse_line(const char* line, size_t len, void* ctx,
     subprocess.check_call(["g++", "-shared", "-fPIC", "-O1", "-o", str(so), str(src)])
     BoxWrapper.reset_instance()
     box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=0, world_size=1)
-    box.initialize_gpu_and_load_model({})
+    box.initialize_gpu_and_load_model({}, slot_omit_in_feedpass=["input_off"])
     try:
         (tmp_path / "index-0").write_text("qa\t1 2\nqb\t3 4\n")
         (tmp_path / "d.txt").write_text("1 qb 11\n0 zz 12\n1 qa 13\n")
@@ -329,8 +329,9 @@ extern "C" int pbx_parse_line(const char* line, size_t len, void* ctx,
         ds.load_into_memory()
         assert ds.get_memory_data_size() == 3 and ds.input_table.miss == 1
         ds._native.prepare_train(1, False, 0, 0)
-        offs = sorted(int(k) for k in ds.unique_keys().tolist() if int(k) in (1, 2))
-        assert offs == [1, 2]
+        # the offset slot is named in slot_omit_in_feedpass: its values are not parameter-server keys
+        assert sorted(ds.unique_keys().tolist()) == [0, 11, 12, 13]
+        assert sorted(box._pass_keys.tolist()) == [0, 11, 12, 13]
         rows = ds.input_table.lookup_input(torch.tensor([2, 0, 1]))
         assert torch.allclose(rows, torch.tensor([[3., 4.], [0., 0.], [1., 2.]]))
     finally:
