@@ -254,3 +254,39 @@ def test_lr_map_sets_per_parameter_rates_of_the_async_dense_table():
         assert (tr.store.flat[mask] != others_before[mask]).float().mean() > 0.5
     finally:
         BoxWrapper.reset_instance()
+
+
+def test_donefile_manifest_and_resume(tmp_path, box):
+    from paddlebox_b200.utils.donefile import ModelManifest, resume
+    man = ModelManifest(str(tmp_path / "models"))
+    assert man.latest() == (None, [])
+    keys = np.arange(1, 21, dtype=np.uint64)
+    rows = box.host_table.fetch_rows(keys)
+    rows[:, 0], rows[:, 2] = 5, 1.0
+    box.host_table.store_rows(keys, rows)
+    box.save_delta(str(tmp_path / "d_old"))
+    man.record_delta("20240101", 9, str(tmp_path / "d_old"))             # older than the base: ignored on resume
+    box.save_base(str(tmp_path / "batch"), str(tmp_path / "xbox"), "20240102")
+    man.record_base("20240102", str(tmp_path / "xbox"), str(tmp_path / "batch"))
+    for p, w in ((1, 2.0), (2, 3.0)):
+        rows[:5 * p, 2] = w
+        box.host_table.store_rows(keys[:5 * p], rows[:5 * p])
+        box.save_delta(str(tmp_path / f"d{p}"))
+        man.record_delta("20240102", p, str(tmp_path / f"d{p}"))
+    want = box.host_table.pull(keys)
+    base, deltas = man.latest()
+    assert base["day"] == "20240102" and [d["pass_id"] for d in deltas] == [1, 2]
+    with open(os.path.join(man.root, "xbox_patch_done.txt"), "a") as f:
+        f.write('{"id": "torn')                                            # a crash mid-append
+    assert [d["pass_id"] for d in man.latest()[1]] == [1, 2]
+    BoxWrapper.reset_instance()
+    b2 = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=0, world_size=1)
+    b2.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0})
+    got = resume(b2, man)
+    assert got["base"].endswith("batch") and len(got["deltas"]) == 2 and got["rows"] == 20 + 5 + 10
+    assert torch.allclose(b2.host_table.pull(keys), want, atol=1e-6)
+    BoxWrapper.reset_instance()
+    b3 = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=0, world_size=1)
+    b3.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0})
+    assert resume(b3, man, serving=True)["base"].endswith("xbox")
+    assert torch.allclose(b3.host_table.pull(keys), want, atol=1e-6)
