@@ -67,6 +67,28 @@ def main():
             dt = time.time() - t0
         out["pack"] = {"batches_per_s": round(nb / dt, 1), "keys_per_s": round(nk / dt), "batches": nb,
                        "keys_per_batch": round(nk / max(nb, 1))}
+        # pass file: the prepared pass written as-is and mapped back (no decode, no key collection)
+        pf = os.path.join(tmp, "pass.arena")
+        t0 = time.time()
+        ds.save_pass_file(pf)
+        t_save = time.time() - t0
+        ds2 = DatasetFactory().create_dataset("InMemoryDataset")
+        ds2.set_use_var(slot_vars(a.slots, a.dense))
+        ds2.set_batch_size(a.batch)
+        t0 = time.time()
+        ds2.load_pass_file(pf)
+        ds2.prepare_train(1)
+        t_load = time.time() - t0
+        t0 = time.time()
+        nb2 = 0
+        for hb in ds2.host_batches():
+            nb2 += 1
+            hb.release()
+        t_pack = time.time() - t0
+        out["pass_file"] = {"MB": round(os.path.getsize(pf) / 1e6, 1), "save_instances_per_s": round(n / t_save),
+                            "load_and_prepare_instances_per_s": round(n / t_load),
+                            "pack_batches_per_s_from_mapping": round(nb2 / max(t_pack, 1e-9), 1)}
+        ds2.release_memory()
     # host tier
     tab = HostTable(embedx_dim=16)
     keys = np.unique(np.random.default_rng(0).integers(1, 1 << 40, 1_000_000, dtype=np.uint64))

@@ -167,6 +167,8 @@ int pbh_dataset_set_str(void* h, const char* key, const char* v) {
   else { pbh::set_error("unknown dataset option %s", key); return -1; }
   return 0;
 }
+int pbh_dataset_save_arena(void* h, const char* path) { return ((Dataset*)h)->save_arena(path); }
+int pbh_dataset_load_arena(void* h, const char* path) { return ((Dataset*)h)->load_arena(path); }
 int pbh_dataset_set_omit_slots(void* h, const int* slot_indices, int n) {
   ((Dataset*)h)->omit_slots.assign(slot_indices, slot_indices + n);
   return 0;

@@ -643,6 +643,7 @@ void Dataset::release_memory() {
 }
 
 void Dataset::local_shuffle(uint64_t seed) {
+  if (arena_only_) return;          // fixed record order; prepare_train shuffles the batches
   drop_arena();
   std::mt19937_64 rng(seed);
   std::shuffle(records_.begin(), records_.end(), rng);
@@ -652,6 +653,7 @@ void Dataset::local_shuffle(uint64_t seed) {
 // slot in place, to measure how much the model relies on those slots
 // (reference RecordReplace / slots_shuffle, data_feed.h:1772-1962, box_wrapper.cc:212-368).
 int Dataset::slots_shuffle(const std::vector<int>& slot_idx, uint64_t seed, bool inverse) {
+  PBH_REQUIRE(!arena_only_, "slots_shuffle needs records: not available for a pass loaded from a pass file");
   const bool had_arena = arena_ok_;
   drop_arena();
   const size_t n = records_.size();
@@ -700,6 +702,7 @@ int Dataset::slots_shuffle(const std::vector<int>& slot_idx, uint64_t seed, bool
 // conflicting); of a float slot the first non-empty, non-zero copy wins.  Returns the number of
 // dropped instances.
 int64_t Dataset::merge_by_ins_id(int merge_size) {
+  if (arena_only_) return 0;        // a pass file holds no instance ids
   drop_arena();
   std::stable_sort(records_.begin(), records_.end(),
                    [](const SlotRecord* a, const SlotRecord* b) { return a->ins_id < b->ins_id; });
@@ -762,6 +765,12 @@ int64_t Dataset::merge_by_ins_id(int merge_size) {
 
 void Dataset::drop_arena() {
   arena_ok_ = false;
+  if (map_base_) munmap(map_base_, map_size_);
+  map_base_ = nullptr;
+  map_size_ = 0;
+  arena_only_ = false;
+  arena_n_ = 0;
+  pk_ = nullptr; pko_ = nullptr; pso_ = nullptr; pd_ = nullptr;
   std::vector<uint64_t>().swap(ar_keys_);
   std::vector<int64_t>().swap(ar_koff_);
   std::vector<uint32_t>().swap(ar_soff_);
@@ -796,11 +805,122 @@ void Dataset::build_arena() {
       }
     }
   });
+  pk_ = ar_keys_.data(); pko_ = ar_koff_.data(); pso_ = ar_soff_.data(); pd_ = ar_dense_.data();
+  arena_n_ = (int64_t)n;
   arena_ok_ = true;
+}
+
+// ---- pass file ------------------------------------------------------------------------------------
+namespace {
+struct ArenaHeader {
+  char magic[8];            // "PBXARENA"
+  uint32_t version, S, dense_dim, reserved;
+  int64_t n, nkeys, n_unique;
+  int64_t off_koff, off_soff, off_dense, off_keys, off_unique, file_size;
+};
+inline int64_t align64(int64_t x) { return (x + 63) / 64 * 64; }
+}  // namespace
+
+int Dataset::save_arena(const std::string& path) {
+  PBH_REQUIRE(!arena_only_, "this pass was loaded from a pass file already");
+  if (!arena_ok_) {
+    const int keep = compact_batches;
+    compact_batches = 2;
+    build_arena();
+    compact_batches = keep;
+  }
+  PBH_REQUIRE(arena_ok_, "no records to save");
+  ArenaHeader h;
+  memset(&h, 0, sizeof(h));
+  memcpy(h.magic, "PBXARENA", 8);
+  h.version = 1; h.S = (uint32_t)n_used_u64_; h.dense_dim = (uint32_t)dense_dim_;
+  h.n = arena_n_; h.nkeys = pko_[arena_n_]; h.n_unique = (int64_t)unique_keys_.size();
+  h.off_koff = align64(sizeof(h));
+  h.off_soff = align64(h.off_koff + (h.n + 1) * 8);
+  h.off_dense = align64(h.off_soff + h.n * (int64_t)(h.S + 1) * 4);
+  h.off_keys = align64(h.off_dense + h.n * (int64_t)h.dense_dim * 4);
+  h.off_unique = align64(h.off_keys + h.nkeys * 8);
+  h.file_size = h.off_unique + h.n_unique * 8;
+  FILE* fp = fopen(path.c_str(), "wb");
+  PBH_REQUIRE(fp != nullptr, "cannot open %s for writing", path.c_str());
+  bool ok = true;
+  auto put = [&](int64_t off, const void* p, size_t bytes) {
+    ok = ok && fseek(fp, (long)off, SEEK_SET) == 0 && (bytes == 0 || fwrite(p, 1, bytes, fp) == bytes);
+  };
+  put(0, &h, sizeof(h));
+  put(h.off_koff, pko_, (size_t)(h.n + 1) * 8);
+  put(h.off_soff, pso_, (size_t)h.n * (h.S + 1) * 4);
+  put(h.off_dense, pd_, (size_t)h.n * h.dense_dim * 4);
+  put(h.off_keys, pk_, (size_t)h.nkeys * 8);
+  put(h.off_unique, unique_keys_.data(), (size_t)h.n_unique * 8);
+  if (ok && h.n_unique == 0) ok = ftruncate(fileno(fp), (off_t)h.file_size) == 0;
+  ok = (fclose(fp) == 0) && ok;
+  PBH_REQUIRE(ok, "short write to %s", path.c_str());
+  return 0;
+}
+
+int Dataset::load_arena(const std::string& path) {
+  if (slot_to_sparse_.size() != slots.size()) finalize_slots();
+  release_memory();
+  int fd = open(path.c_str(), O_RDONLY);
+  PBH_REQUIRE(fd >= 0, "cannot open %s", path.c_str());
+  struct stat st;
+  if (fstat(fd, &st) != 0 || (size_t)st.st_size < sizeof(ArenaHeader)) { close(fd); PBH_REQUIRE(false, "%s is not a pass file", path.c_str()); }
+  void* base = mmap(nullptr, (size_t)st.st_size, PROT_READ, MAP_PRIVATE, fd, 0);
+  close(fd);
+  PBH_REQUIRE(base != MAP_FAILED, "cannot map %s", path.c_str());
+  const ArenaHeader& h = *(const ArenaHeader*)base;
+  const bool good = memcmp(h.magic, "PBXARENA", 8) == 0 && h.version == 1 && h.file_size <= (int64_t)st.st_size &&
+                    h.n >= 0 && h.nkeys >= 0 && h.off_unique + h.n_unique * 8 <= (int64_t)st.st_size;
+  if (!good || (int)h.S != n_used_u64_ || (int)h.dense_dim != dense_dim_) {
+    const uint32_t fs = good ? h.S : 0, fd_ = good ? h.dense_dim : 0;
+    munmap(base, (size_t)st.st_size);
+    PBH_REQUIRE(good, "%s is not a pass file (bad header)", path.c_str());
+    PBH_REQUIRE(false, "pass file %s holds %u sparse slots / dense width %u, the dataset is set up for %d / %d",
+                path.c_str(), fs, fd_, n_used_u64_, dense_dim_);
+  }
+  const char* b = (const char*)base;
+  map_base_ = base;
+  map_size_ = (size_t)st.st_size;
+  pko_ = (const int64_t*)(b + h.off_koff);
+  pso_ = (const uint32_t*)(b + h.off_soff);
+  pd_ = (const float*)(b + h.off_dense);
+  pk_ = (const uint64_t*)(b + h.off_keys);
+  arena_n_ = h.n;
+  arena_only_ = true;
+  arena_ok_ = true;
+  const uint64_t* uk = (const uint64_t*)(b + h.off_unique);
+  unique_keys_.assign(uk, uk + h.n_unique);
+  total_feasigns_ = h.nkeys;
+  lines_read_ = h.n;
+  madvise(base, map_size_, MADV_WILLNEED);
+  return 0;
 }
 
 int Dataset::prepare_train(int nworkers, bool shuffle, uint64_t seed, int64_t min_batches) {
   PBH_REQUIRE(nworkers >= 1, "nworkers must be >= 1");
+  if (arena_only_) {
+    // the record order of a pass file is fixed (it was shuffled before it was saved): a shuffle request
+    // permutes the batches instead
+    worker_batches_.assign(nworkers, {});
+    if (arena_n_ < nworkers) return 0;
+    std::vector<BatchRange> all;
+    compute_batch_ranges(arena_n_, batch_size, nworkers, &all);
+    if (shuffle) {
+      // whole rounds of nworkers batches move together so that every worker keeps equal-sized batches
+      const size_t rounds = all.size() / (size_t)nworkers;
+      std::vector<size_t> perm(rounds);
+      for (size_t i = 0; i < rounds; ++i) perm[i] = i;
+      std::mt19937_64 rng(seed);
+      std::shuffle(perm.begin(), perm.end(), rng);
+      std::vector<BatchRange> mixed;
+      for (size_t r : perm) mixed.insert(mixed.end(), all.begin() + r * nworkers, all.begin() + (r + 1) * nworkers);
+      mixed.insert(mixed.end(), all.begin() + rounds * nworkers, all.end());
+      all.swap(mixed);
+    }
+    for (size_t i = 0; i < all.size(); ++i) worker_batches_[i % nworkers].push_back(all[i]);
+    return 0;
+  }
   if (enable_pv_merge) {
     // page-view merge: instances of one search_id stay adjacent, ordered by rank (data_set.cc:2648-2688)
     std::stable_sort(records_.begin(), records_.end(), [](const SlotRecord* a, const SlotRecord* b) {
@@ -839,7 +959,7 @@ int Dataset::batch_shape(int worker, int64_t b, int* B, int64_t* n_keys) const {
                   b < (int64_t)worker_batches_[worker].size(), "batch (%d, %lld) out of range", worker, (long long)b);
   const BatchRange& r = worker_batches_[worker][b];
   int64_t nk = 0;
-  if (arena_ok_) nk = ar_koff_[r.start + r.len] - ar_koff_[r.start];
+  if (arena_ok_) nk = pko_[r.start + r.len] - pko_[r.start];
   else for (int i = 0; i < r.len; ++i) nk += (int64_t)records_[r.start + i]->u64_vals.size();
   *B = r.len;
   *n_keys = nk;
@@ -853,17 +973,33 @@ int Dataset::pack_batch(int worker, int64_t b, uint64_t* keys, int32_t* off, flo
   const int B = r.len, S = n_used_u64_;
   if (arena_ok_ && !slot_major) {
     // compact arena: three contiguous copies
-    const int64_t k0 = ar_koff_[r.start];
-    memcpy(keys, ar_keys_.data() + k0, (size_t)(ar_koff_[r.start + B] - k0) * sizeof(uint64_t));
-    const uint32_t* so = ar_soff_.data() + (size_t)r.start * (S + 1);
+    const int64_t k0 = pko_[r.start];
+    memcpy(keys, pk_ + k0, (size_t)(pko_[r.start + B] - k0) * sizeof(uint64_t));
+    const uint32_t* so = pso_ + (size_t)r.start * (S + 1);
     for (int i = 0; i < B; ++i) {
-      const int32_t base = (int32_t)(ar_koff_[r.start + i] - k0);
+      const int32_t base = (int32_t)(pko_[r.start + i] - k0);
       int32_t* o = off + (int64_t)i * (S + 1);
       const uint32_t* si = so + (size_t)i * (S + 1);
       for (int s = 0; s <= S; ++s) o[s] = base + (int32_t)si[s];
     }
     if (dense && dense_dim_ > 0)
-      memcpy(dense, ar_dense_.data() + (size_t)r.start * dense_dim_, (size_t)B * dense_dim_ * sizeof(float));
+      memcpy(dense, pd_ + (size_t)r.start * dense_dim_, (size_t)B * dense_dim_ * sizeof(float));
+    return 0;
+  }
+  if (arena_only_) {
+    // slot-major straight from the mapped pass file
+    int64_t cur = 0;
+    for (int s = 0; s < S; ++s) {
+      for (int i = 0; i < B; ++i) {
+        const uint32_t* si = pso_ + (size_t)(r.start + i) * (S + 1);
+        off[(int64_t)s * B + i] = (int32_t)cur;
+        memcpy(keys + cur, pk_ + pko_[r.start + i] + si[s], (size_t)(si[s + 1] - si[s]) * sizeof(uint64_t));
+        cur += si[s + 1] - si[s];
+      }
+    }
+    off[(int64_t)S * B] = (int32_t)cur;
+    if (dense && dense_dim_ > 0)
+      memcpy(dense, pd_ + (size_t)r.start * dense_dim_, (size_t)B * dense_dim_ * sizeof(float));
     return 0;
   }
   if (!slot_major) {
@@ -907,6 +1043,7 @@ int Dataset::batch_ins_ids(int worker, int64_t b, std::string* joined) const {
                   b < (int64_t)worker_batches_[worker].size(), "batch out of range");
   const BatchRange& r = worker_batches_[worker][b];
   joined->clear();
+  PBH_REQUIRE(!arena_only_, "a pass file holds no instance ids");
   for (int i = 0; i < r.len; ++i) {
     if (i) joined->push_back('\n');
     joined->append(records_[r.start + i]->ins_id);
@@ -918,6 +1055,7 @@ int Dataset::batch_meta(int worker, int64_t b, uint64_t* search_ids, uint32_t* r
   PBH_REQUIRE(worker >= 0 && worker < (int)worker_batches_.size() && b >= 0 &&
                   b < (int64_t)worker_batches_[worker].size(), "batch out of range");
   const BatchRange& r = worker_batches_[worker][b];
+  PBH_REQUIRE(!arena_only_, "a pass file holds no search_id / rank / cmatch");
   for (int i = 0; i < r.len; ++i) {
     const SlotRecord* rec = records_[r.start + i];
     if (search_ids) search_ids[i] = rec->search_id;
@@ -960,6 +1098,7 @@ static int write_archive(const std::string& path, const std::vector<const SlotRe
 }
 
 int Dataset::save_archive(const std::string& path) const {
+  PBH_REQUIRE(!arena_only_, "save_archive needs records: not available for a pass loaded from a pass file");
   std::vector<const SlotRecord*> all(records_.begin(), records_.end());
   return write_archive(path, all);
 }
@@ -970,6 +1109,7 @@ int Dataset::save_archive(const std::string& path) const {
 // data_set.cc:2422-2547).  mode 0 = random, 1 = search_id, 2 = hash of ins_id.
 int Dataset::save_partitioned(const std::string& prefix, int nparts, int mode, uint64_t seed) const {
   PBH_REQUIRE(nparts >= 1, "nparts must be >= 1");
+  PBH_REQUIRE(!arena_only_, "global shuffle needs records: not available for a pass loaded from a pass file");
   std::vector<std::vector<const SlotRecord*>> parts(nparts);
   std::mt19937_64 rng(seed + (uint64_t)rank * 0x9E3779B97F4A7C15ull);
   for (const SlotRecord* r : records_) {

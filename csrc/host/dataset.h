@@ -124,7 +124,12 @@ class Dataset {
   int64_t merge_by_ins_id(int merge_size);   // merge records sharing an ins_id; returns dropped instances
   int slots_shuffle(const std::vector<int>& slot_idx, uint64_t seed, bool inverse = false);  // AUC runner: permute slots across records
   int prepare_train(int nworkers, bool shuffle, uint64_t seed, int64_t min_batches);
-  int64_t num_records() const { return (int64_t)records_.size(); }
+  int64_t num_records() const { return arena_only_ ? arena_n_ : (int64_t)records_.size(); }
+  // Pass file: the compact arena (and the pass's unique keys) written as-is and mapped back with no
+  // per-record decode — a pre-processed pass loads at page-cache speed (role: the reference's
+  // PreLoadIntoDisk / archive mode, data_set.cc:2092-2217, which still deserialises record by record).
+  int save_arena(const std::string& path);
+  int load_arena(const std::string& path);
   int64_t num_batches(int worker) const { return worker < (int)worker_batches_.size() ? (int64_t)worker_batches_[worker].size() : 0; }
   // sizes of one batch: instances and total uint64 feasigns of used sparse slots
   int batch_shape(int worker, int64_t b, int* B, int64_t* n_keys) const;
@@ -166,6 +171,16 @@ class Dataset {
   std::vector<int64_t> ar_koff_;     // [n + 1] first feasign of every record
   std::vector<uint32_t> ar_soff_;    // [n * (S + 1)] slot offsets inside the record
   std::vector<float> ar_dense_;      // [n * dense_dim] densified float slots
+  // what pack_batch reads: the vectors above, or a pass file mapped by load_arena (arena_only_: there
+  // are no SlotRecords then; record-level operations are refused)
+  const uint64_t* pk_ = nullptr;
+  const int64_t* pko_ = nullptr;
+  const uint32_t* pso_ = nullptr;
+  const float* pd_ = nullptr;
+  bool arena_only_ = false;
+  int64_t arena_n_ = 0;
+  void* map_base_ = nullptr;
+  size_t map_size_ = 0;
   void build_arena();
   void drop_arena();
   std::mutex rec_mu_;

@@ -110,6 +110,12 @@ uint64_t pbh_input_index_add(void* ix, const char* key, size_t len, int* fresh);
 uint64_t pbh_input_index_get(void* ix, const char* key, size_t len);
 uint64_t pbh_input_index_size(void* ix);
 uint64_t pbh_input_index_miss(void* ix);
+/* pass file: the compact arena + unique keys of a prepared pass written as-is; load maps it back with no
+ * per-record decode (role of PreLoadIntoDisk / archive mode, data_set.cc:2092-2217).  The loading
+ * dataset must have the same used slots; record-level operations (slots_shuffle, ins ids, PV meta,
+ * global shuffle) are refused on such a pass. */
+int pbh_dataset_save_arena(void* ds, const char* path);
+int pbh_dataset_load_arena(void* ds, const char* path);
 int pbh_dataset_set_input_index(void* ds, void* ix);
 /* slots (indices in set_slots order) whose feasigns are not PS keys: skipped by the key collection
  * (slot_omit_in_feedpass of InitializeGPUAndLoadModel, data_feed.cc:3119-3146) */

@@ -448,6 +448,20 @@ class InMemoryDataset(DatasetBase):
     def wait_load_disk_done(self):
         self._native.load_archive(self._archive)
 
+    # pass files: a prepared pass written as-is, mapped back with no decode ---------------------------
+    def save_pass_file(self, path: str):
+        """Write the loaded pass (in its current order: call ``local_shuffle`` / ``prepare_train`` first
+        for a shuffled file) and its unique keys as one pass file.  A later ``load_pass_file`` maps it
+        back at page-cache speed — no text parse, no per-record decode, no key collection."""
+        self._native.save_arena(path)
+
+    def load_pass_file(self, path: str):
+        """Make the pass file the loaded pass (the dataset must use the same slots).  The instance order
+        is the file's; ``prepare_train(shuffle=True)`` permutes whole batches.  Instance ids, PV fields and
+        record-level shuffles are not available on such a pass."""
+        self._native.load_arena(path)
+        self._prepared_workers = 0
+
     # training iteration ---------------------------------------------------------------------------
     def prepare_train(self, num_workers: int = 1, worker: int = 0, shuffle: bool | None = None,
                       min_batches: int = 0):
@@ -561,6 +575,10 @@ class BoxPSDataset(InMemoryDataset):
 
     def wait_feed_pass_done(self):
         self.wait_preload_done()
+
+    def load_pass_file(self, path: str):
+        super().load_pass_file(path)
+        self._feed_keys()
 
     def read_ins_into_memory(self):
         """``BoxHelper::ReadData2Memory``: BeginFeedPass -> LoadIntoMemory -> EndFeedPass."""

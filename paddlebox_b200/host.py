@@ -400,6 +400,12 @@ class NativeDataset:
             N.host().pbh_dataset_unique_keys(self._h, _u64p(out), C.c_int64(n))
         return out
 
+    def save_arena(self, path: str):
+        N.hcheck(N.host().pbh_dataset_save_arena(self._h, path.encode()), "pbh_dataset_save_arena")
+
+    def load_arena(self, path: str):
+        N.hcheck(N.host().pbh_dataset_load_arena(self._h, path.encode()), "pbh_dataset_load_arena")
+
     def save_archive(self, path: str):
         N.hcheck(N.host().pbh_dataset_save_archive(self._h, path.encode()))
 

@@ -546,3 +546,53 @@ def test_fast_float_parser_matches_float32(tmp_path):
     want = np.array([np.float32(float(v)) for v in vals], dtype=np.float32)
     got = b.dense[0].numpy()
     assert np.array_equal(got, want), np.flatnonzero(got != want)
+
+
+def test_pass_file_roundtrip_is_batch_identical(tmp_path):
+    """save_pass_file / load_pass_file: same batches (both layouts), same unique keys, no records needed."""
+    import time
+    from paddlebox_b200.dataset import DatasetFactory
+    files = write_files(str(tmp_path), n_files=2, lines_per_file=300, n_sparse=5, n_dense=3, key_space=200)
+
+    def make():
+        ds = DatasetFactory().create_dataset("InMemoryDataset")
+        ds.set_use_var(slot_vars(5, 3))
+        ds.set_batch_size(32)
+        ds.set_thread(2)
+        return ds
+
+    a = make()
+    a.set_filelist(files)
+    a.load_into_memory()
+    a.prepare_train(2, 0, shuffle=True)
+    want = {w: [(b.keys.clone(), b.lod.clone(), b.dense.clone()) for b in a.batches(worker=w)] for w in (0, 1)}
+    a.save_pass_file(str(tmp_path / "pass.arena"))
+    b = make()
+    b.load_pass_file(str(tmp_path / "pass.arena"))
+    assert b.get_memory_data_size() == 600 and np.array_equal(np.sort(b.unique_keys()), np.sort(a.unique_keys()))
+    b.prepare_train(2, 0, shuffle=False)
+    for w in (0, 1):
+        got = list(b.batches(worker=w))
+        assert len(got) == len(want[w])
+        for g, (k, l, d) in zip(got, want[w]):
+            assert torch.equal(g.keys, k) and torch.equal(g.lod, l) and torch.equal(g.dense, d)
+    # record-major staging buffers (the pipelined feed's input) agree as well
+    ha = [(h.n_keys, h.batch_size) for h in a.host_batches(worker=0)]
+    hb = [(h.n_keys, h.batch_size) for h in b.host_batches(worker=0)]
+    assert ha == hb and len(ha) > 0
+    # a shuffle permutes whole batches: same multiset of batches
+    b.prepare_train(2, 0, shuffle=True)
+    sums = sorted(int(x.keys.sum()) for w in (0, 1) for x in b.batches(worker=w))
+    assert sums == sorted(int(k.sum()) for w in (0, 1) for k, _, _ in want[w])
+    # record-level operations are refused, a wrong slot set too
+    with pytest.raises(N.NativeError):
+        b._native.slots_shuffle([0], 1)
+    c = DatasetFactory().create_dataset("InMemoryDataset")
+    c.set_use_var(slot_vars(4, 3))
+    with pytest.raises(N.NativeError, match="sparse slots"):
+        c.load_pass_file(str(tmp_path / "pass.arena"))
+    # loading text again replaces the mapped pass
+    b.set_filelist(files[:1])
+    b.load_into_memory()
+    assert b.get_memory_data_size() == 300
+    b.release_memory()
