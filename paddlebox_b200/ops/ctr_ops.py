@@ -172,14 +172,39 @@ def partial_sum(inputs, start_index: int = 0, length: int = -1) -> torch.Tensor:
     return torch.stack(outs, 0).sum(0)
 
 
-def fused_seqpool_concat(pooled: torch.Tensor, num_slots: int, offsets=None, dims=None) -> torch.Tensor:
-    """Select ``dims[i]`` columns starting at ``offsets[i]`` from every slot block of a pooled
-    tensor [B, S*E] and concatenate (reference fused_seqpool_concat, fused_concat_op.cu)."""
-    E = pooled.shape[1] // num_slots
-    blocks = pooled.view(pooled.shape[0], num_slots, E)
-    if offsets is None:
-        return pooled
-    return torch.cat([blocks[:, :, o:o + d].reshape(pooled.shape[0], -1) for o, d in zip(offsets, dims)], 1)
+def fused_seqpool_concat(inputs, num_slots: int, offsets=None, dims=None, lod: torch.Tensor | None = None,
+                         batch_size: int | None = None) -> torch.Tensor:
+    """``fluid.contrib.layers.fused_seqpool_concat`` (contrib/layers/nn.py:2726-2800, fused_concat_op.cu):
+    two groups of per-slot sequence embeddings are SUM-pooled by ``lod`` and, slot by slot, the columns
+    ``[offsets[g], offsets[g] + dims[g])`` of group g are laid side by side.
+
+    ``inputs``: a pair ``[x1, x2]`` of ``[N, E_g]`` tensors in slot-major bag order sharing ``lod``
+    (int32 ``[S*B+1]``) -> ``[B, S * (dims[0] + dims[1])]``; ``dims[g] <= 0`` means "to the end".
+    A single already pooled tensor ``[B, S*E]`` is also accepted: every ``(offset, dim)`` pair then selects
+    a column range of each slot block (the selections are concatenated group after group)."""
+    if torch.is_tensor(inputs):
+        pooled = inputs
+        E = pooled.shape[1] // num_slots
+        blocks = pooled.view(pooled.shape[0], num_slots, E)
+        if offsets is None:
+            return pooled
+        return torch.cat([blocks[:, :, o:o + d].reshape(pooled.shape[0], -1) for o, d in zip(offsets, dims)], 1)
+    if len(inputs) != 2:
+        raise ValueError("fused_seqpool_concat takes exactly two input groups")
+    assert lod is not None and batch_size is not None, "sequence inputs need lod and batch_size"
+    B, S = batch_size, num_slots
+    lens = (lod[1:] - lod[:-1]).long()
+    n = int(lod[-1])
+    bag = torch.repeat_interleave(torch.arange(S * B, device=lod.device), lens, output_size=n)
+    parts = []
+    for g, x in enumerate(inputs):
+        start = max(0, offsets[g]) if isinstance(offsets, (list, tuple)) and g < len(offsets) else 0
+        dim = dims[g] if isinstance(dims, (list, tuple)) and g < len(dims) else 0
+        if dim <= 0:
+            dim = x.shape[1] - start
+        pooled = torch.zeros(S * B, dim, dtype=x.dtype, device=x.device).index_add_(0, bag, x[:n, start:start + dim])
+        parts.append(pooled.view(S, B, dim))
+    return torch.cat(parts, 2).permute(1, 0, 2).reshape(B, -1)
 
 
 def fused_seq_tensor(x: torch.Tensor, ad_input: torch.Tensor, batch_count: int, max_length: int, slot_num: int,

@@ -290,3 +290,28 @@ def test_donefile_manifest_and_resume(tmp_path, box):
     b3.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0})
     assert resume(b3, man, serving=True)["base"].endswith("xbox")
     assert torch.allclose(b3.host_table.pull(keys), want, atol=1e-6)
+
+
+def test_fused_seqpool_concat_two_groups():
+    from paddlebox_b200.ops.ctr_ops import fused_seqpool_concat
+    gen = torch.Generator().manual_seed(0)
+    B, S = 4, 3
+    lens = torch.randint(0, 3, (S * B,), generator=gen)
+    lod = torch.zeros(S * B + 1, dtype=torch.int32)
+    lod[1:] = torch.cumsum(lens, 0)
+    n = int(lod[-1])
+    x1 = torch.rand(n, 6, generator=gen, requires_grad=True)
+    x2 = torch.rand(n, 5, generator=gen)
+    out = fused_seqpool_concat([x1, x2], S, offsets=[1, 2], dims=[3, 0], lod=lod, batch_size=B)
+    assert out.shape == (B, S * (3 + 3))
+    ll = lod.tolist()
+    for s in range(S):
+        for b in range(B):
+            g = s * B + b
+            want = torch.cat([x1[ll[g]:ll[g + 1], 1:4].sum(0), x2[ll[g]:ll[g + 1], 2:5].sum(0)])
+            assert torch.allclose(out[b, s * 6:(s + 1) * 6], want, atol=1e-6)
+    out.sum().backward()
+    assert torch.all(x1.grad[:, 1:4] == 1) and torch.all(x1.grad[:, 0] == 0) and torch.all(x1.grad[:, 4:] == 0)
+    pooled = torch.arange(24.).view(2, 12)
+    sel = fused_seqpool_concat(pooled, 3, offsets=[0, 2], dims=[1, 2])
+    assert sel.shape == (2, 3 + 6) and sel[0].tolist() == [0, 4, 8, 2, 3, 6, 7, 10, 11]
