@@ -154,7 +154,7 @@ def fused_concat(inputs, start_index: int = 0, length: int = -1, axis: int = 1) 
     fused_concat_op.cu:34-258)."""
     outs = []
     for t in inputs:
-        s = start_index if start_index >= 0 else t.shape[1] + start_index
+        s = max(start_index, 0)                       # the layer clamps a negative start to 0 (nn.py:2822)
         e = t.shape[1] if length < 0 else s + length
         outs.append(t[:, s:e])
     return torch.cat(outs, dim=axis)
@@ -209,20 +209,33 @@ def fused_seqpool_concat(inputs, num_slots: int, offsets=None, dims=None, lod: t
 
 def fused_seq_tensor(x: torch.Tensor, ad_input: torch.Tensor, batch_count: int, max_length: int, slot_num: int,
                      fea_emb_dim: int, ad_slot_num: int, ad_slot_offset: int = 0):
-    """DIN-style history tensor builder (reference fused_seq_tensor_op.cu:14-147): reshape the
-    user-behaviour embeddings ``x`` [ins*batch_count, slot_num*max_length*dim] into
-    (din_out [ins, batch_count*max_length, (slot_num + ad_slot_num)... ], mask, side info).
-    Returns ``(din, mask, side, ad_slot_session)`` with the ad slots broadcast along time."""
-    ins = x.shape[0] // batch_count
-    seq = x.view(ins, batch_count, slot_num, max_length, fea_emb_dim)
-    mask = (seq.abs().sum(dim=(2, 4)) > 0).to(x.dtype)                     # [ins, batch_count, max_length]
-    ad = ad_input.view(ins, batch_count, -1, fea_emb_dim)[:, :, ad_slot_offset:ad_slot_offset + ad_slot_num]
-    ad_b = ad[:, :, :, None, :].expand(ins, batch_count, ad_slot_num, max_length, fea_emb_dim)
-    din = torch.cat([seq[:, :, :ad_slot_num] if slot_num >= ad_slot_num else seq, ad_b], dim=2)
-    din = din.permute(0, 1, 3, 2, 4).reshape(ins, batch_count, max_length, -1)
-    side = seq[:, :, ad_slot_num:].permute(0, 1, 3, 2, 4).reshape(ins, batch_count, max_length, -1)
-    ad_sess = ad_b.permute(0, 1, 3, 2, 4).reshape(ins, batch_count, max_length, -1)
-    return din, mask, side, ad_sess
+    """DIN-style sequence tensors (``fluid.contrib.layers.fused_seq_tensor``; kernels
+    fused_seq_tensor_op.cu:14-290).
+
+    ``x`` ``[ins, batch_count * slot_num * max_length * dim]``: per instance and session the behaviour
+    embeddings laid out ``[slot][time][dim]``; ``ad_input`` ``[ins, batch_count * ad_slot_num * dim]``: the
+    candidate ad's embeddings of the ``ad_slot_num`` slots that start at ``ad_slot_offset``.  Returns, all
+    session-major ``[batch_count, ins, max_length, ...]``:
+
+    * ``din``  ``[..., 4 * ad_slot_num * dim]`` = ``[seq, ad, seq - ad, seq * ad]`` of the ad slots,
+    * ``mask`` ``[batch_count, ins, max_length]`` = 1 where the time step holds any non-zero value
+      (``|sum over slots and dims| > 1e-8``),
+    * ``side`` ``[..., (slot_num - ad_slot_num) * dim]`` = the remaining (side-info) slots — those after the
+      ad slots when ``ad_slot_offset == 0``, else those from slot 0,
+    * ``ad_slot_session`` ``[..., ad_slot_num * dim]`` = the sequence values of the ad slots."""
+    ins = x.shape[0]
+    bc, L, D, an = batch_count, max_length, fea_emb_dim, ad_slot_num
+    seq = x.reshape(ins, bc, slot_num, L, D)
+    ad = ad_input.reshape(ins, bc, an, D)
+    inp = seq[:, :, ad_slot_offset:ad_slot_offset + an].permute(1, 0, 3, 2, 4)          # [bc, ins, L, an, D]
+    ad_b = ad.permute(1, 0, 2, 3)[:, :, None].expand(bc, ins, L, an, D)
+    sess = inp.reshape(bc, ins, L, an * D)
+    adf = ad_b.reshape(bc, ins, L, an * D)
+    din = torch.cat([sess, adf, sess - adf, sess * adf], dim=-1)
+    so = an if ad_slot_offset == 0 else 0
+    side = seq[:, :, so:so + slot_num - an].permute(1, 0, 3, 2, 4).reshape(bc, ins, L, (slot_num - an) * D)
+    mask = (seq.sum(dim=(2, 4)).abs() > 1e-8).to(x.dtype).permute(1, 0, 2).contiguous()
+    return din, mask, side, sess.contiguous()
 
 
 def shuffle_batch(x: torch.Tensor, seed: int | None = None):

@@ -147,14 +147,33 @@ def test_extended_sparse_rank_attention2_seq_tensor_dedup(box):
     ro = CO.build_rank_offset(torch.tensor([1, 1, 1, 2, 2, 3]), torch.tensor([1, 2, 3, 1, 2, 1]), 3)
     P = torch.rand(9 * 5, 4, generator=gen)
     assert torch.equal(CO.rank_attention2(xr, ro, P, 3), CO.rank_attention(xr, ro, P, 3))
-    # fused_seq_tensor shapes and mask
-    ins, bc, L, sn, d, an = 2, 3, 4, 3, 2, 1
-    xs = torch.rand(ins * bc, sn * L * d, generator=gen)
+    # fused_seq_tensor against an index-by-index restatement of the reference kernels
+    ins, bc, L, sn, d, an, off = 2, 3, 4, 3, 2, 1, 1
+    xs = torch.rand(ins, bc * sn * L * d, generator=gen) + 0.1
     xs.view(ins, bc, sn, L, d)[0, 0, :, 2:] = 0                     # two padded time steps
-    ad = torch.rand(ins * bc, 2 * d, generator=gen)
-    din, mask, side, sess = CO.fused_seq_tensor(xs, ad, bc, L, sn, d, an)
-    assert din.shape == (ins, bc, L, 2 * an * d) and side.shape == (ins, bc, L, (sn - an) * d) and sess.shape == (ins, bc, L, an * d)
-    assert mask[0, 0].tolist() == [1, 1, 0, 0] and mask[1].min() == 1
+    ad = torch.rand(ins, bc * an * d, generator=gen)
+    din, mask, side, sess = CO.fused_seq_tensor(xs, ad, bc, L, sn, d, an, off)
+    assert din.shape == (bc, ins, L, 4 * an * d) and side.shape == (bc, ins, L, (sn - an) * d)
+    assert sess.shape == (bc, ins, L, an * d) and mask.shape == (bc, ins, L)
+    xf, af = xs.reshape(-1), ad.reshape(-1)
+    one_slot, one_seq, piece = L * d, sn * L * d, an * d
+    for b in range(bc):
+        for i in range(ins):
+            for t in range(L):
+                for idx in range(piece):
+                    sl, osl, k = idx // d + off, idx // d, idx % d
+                    v = xf[i * bc * one_seq + b * one_seq + sl * one_slot + t * d + k]
+                    a = af[i * bc * piece + b * piece + osl * d + k]
+                    row = din[b, i, t]
+                    assert row[osl * d + k] == v and row[piece + osl * d + k] == a
+                    assert torch.isclose(row[2 * piece + osl * d + k], v - a) and torch.isclose(row[3 * piece + osl * d + k], v * a)
+                    assert sess[b, i, t, osl * d + k] == v
+                for idx in range((sn - an) * d):
+                    sl, k = idx // d + 0, idx % d                    # ad_slot_offset != 0: side slots start at 0
+                    assert side[b, i, t, idx] == xf[i * bc * one_seq + b * one_seq + sl * one_slot + t * d + k]
+    assert mask[0, 0].tolist() == [1, 1, 0, 0] and mask[:, 1].min() == 1 and mask[1:].min() == 1
+    din0, _, side0, _ = CO.fused_seq_tensor(xs, ad, bc, L, sn, d, an, 0)
+    assert torch.equal(side0[0, 0, 0], xs.view(ins, bc, sn, L, d)[0, 0, 1:, 0].reshape(-1))     # offset 0: side = slots after
     # dedup contract
     k = torch.tensor([9, 3, 9, 1, 3, 9])
     merged, restore, sorted_idx, offset, cnts = R.dedup_keys_and_fillidx(k)
