@@ -128,15 +128,17 @@ def scaled_int8fc(x, w, bias, input_scale_factor=1.0, bias_scale_factor=1.0, wei
 
 # ---------------------------------------------------------------- cross_norm_hadamard
 class CrossNormHadamard(nn.Module):
-    """For ``fields_num`` field pairs (a_i, b_i) of width ``embed_dim`` laid side by side in the
-    input, emit ``[a_i, b_i, a_i*b_i]`` and normalise every output column with data_norm style
-    running summaries (reference cross_norm_hadamard.cu.h:44-240, cross_norm_hadamard_op.cu)."""
+    """For ``fields_num`` field pairs (a_i, b_i) of width ``embed_dim`` laid side by side in the input
+    (``[a_0, b_0, a_1, b_1, ...]``), emit per pair the block ``[a_i, b_i, a_i*b_i, <a_i, b_i>]`` —
+    ``3*embed_dim + 1`` columns, the last one the dot product — and normalise every output column with
+    data_norm style running summaries (reference cross_norm_hadamard.cu.h:44-240: ``nncross_normforward_multi``
+    + ``..._multi_sim``; mean = sum/size, scale = sqrt(size/square_sum))."""
 
     def __init__(self, fields_num: int, embed_dim: int, epsilon: float = 1e-4, summary_decay_rate: float = 0.9999999,
                  sync_stats: bool = False):
         super().__init__()
         self.fields_num, self.embed_dim = fields_num, embed_dim
-        self.norm = F.DataNorm(fields_num * 3 * embed_dim, epsilon, summary_decay_rate, sync_stats,
+        self.norm = F.DataNorm(fields_num * (3 * embed_dim + 1), epsilon, summary_decay_rate, sync_stats,
                                name="cross_norm")
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
@@ -144,7 +146,8 @@ class CrossNormHadamard(nn.Module):
         f, d = self.fields_num, self.embed_dim
         pairs = x.view(B, f, 2, d)
         a, b = pairs[:, :, 0], pairs[:, :, 1]
-        y = torch.cat([a, b, a * b], dim=2).reshape(B, f * 3 * d)
+        had = a * b
+        y = torch.cat([a, b, had, had.sum(2, keepdim=True)], dim=2).reshape(B, f * (3 * d + 1))
         return self.norm(y)
 
 

@@ -155,8 +155,12 @@ def test_batch_fc_scaled_fc_cross_norm_and_slices():
     assert torch.allclose(xi.grad, (torch.ones(8, 4) @ wi.t()) * 2, rtol=3e-2, atol=3e-2)
     assert O.scaled_int8fc(xi.detach(), wi.detach(), bi).shape == (8, 4)
     cn = O.CrossNormHadamard(fields_num=2, embed_dim=3)
-    out = cn(torch.rand(5, 12))
-    assert out.shape == (5, 18)
+    xin = torch.rand(5, 12)
+    out = cn(xin)
+    assert out.shape == (5, 20)
+    # summaries start at size 1e4, sum 0, square_sum 1e4: mean 0, scale 1 -> the raw block [a, b, a*b, <a,b>]
+    a0, b0 = xin[:, 0:3], xin[:, 3:6]
+    assert torch.allclose(out[:, :10], torch.cat([a0, b0, a0 * b0, (a0 * b0).sum(1, keepdim=True)], 1), atol=1e-6)
     a, b2 = torch.arange(12.).reshape(3, 4), torch.arange(12., 24.).reshape(3, 4)
     assert torch.equal(O.partial_concat([a, b2], 1, 2), torch.cat([a[:, 1:3], b2[:, 1:3]], 1))
     assert torch.equal(O.partial_sum([a, b2], 1, 2), a[:, 1:3] + b2[:, 1:3])
