@@ -83,8 +83,29 @@ class BatchFC(nn.Module):
         return batch_fc(x, self.w, self.b, self.act)
 
 
-def batch_fc(x: torch.Tensor, w: torch.Tensor, b: torch.Tensor, act: str | None = None) -> torch.Tensor:
-    y = torch.baddbmm(b[:, None, :], x, w)
+def batch_fc(x: torch.Tensor, w: torch.Tensor, b: torch.Tensor, act: str | None = None, batchcount: int = 0,
+             transpose_weight: bool = False) -> torch.Tensor:
+    """The three layouts of the reference op (batch_fc_op.cc:43-130, batch_fc_op.cu:200-567):
+
+    * default: ``x`` [S, ins, in], ``w`` [S, in, out], ``b`` [S, out] -> [S, ins, out];
+    * ``batchcount`` > 0: ``x`` [ins, bc*in], ``w`` [in, bc*out], ``b`` [1, bc*out] -> [ins, bc*out]; column
+      block k of the output is ``x``'s block k times ``w``'s block k;
+    * ``transpose_weight`` (needs ``batchcount``): ``x`` [bc, ins, in], ``w`` [in, bc*out], ``b`` [1, bc*out]
+      -> [bc, ins, out]."""
+    if transpose_weight:
+        if batchcount <= 0:
+            raise ValueError("with transpose_weight, batchcount should be > 0")
+        bc, out = batchcount, w.shape[1] // batchcount
+        wb = w.view(w.shape[0], bc, out).permute(1, 0, 2)                       # [bc, in, out]
+        y = torch.baddbmm(b.reshape(bc, 1, out), x, wb)
+    elif batchcount > 0:
+        bc, ins = batchcount, x.shape[0]
+        fin, out = x.shape[1] // bc, w.shape[1] // bc
+        xb = x.view(ins, bc, fin).permute(1, 0, 2)                              # [bc, ins, in]
+        wb = w.view(fin, bc, out).permute(1, 0, 2)                              # [bc, in, out]
+        y = torch.baddbmm(b.reshape(bc, 1, out), xb, wb).permute(1, 0, 2).reshape(ins, bc * out)
+    else:
+        y = torch.baddbmm(b[:, None, :], x, w)
     if act == "relu":
         y = torch.relu(y)
     return y

@@ -334,3 +334,23 @@ def test_fused_seqpool_concat_two_groups():
     pooled = torch.arange(24.).view(2, 12)
     sel = fused_seqpool_concat(pooled, 3, offsets=[0, 2], dims=[1, 2])
     assert sel.shape == (2, 3 + 6) and sel[0].tolist() == [0, 4, 8, 2, 3, 6, 7, 10, 11]
+
+
+def test_batch_fc_layouts():
+    from paddlebox_b200.ops.ctr_ops import batch_fc
+    gen = torch.Generator().manual_seed(0)
+    bc, ins, fin, out = 3, 5, 4, 2
+    x2 = torch.rand(ins, bc * fin, generator=gen)
+    w2 = torch.rand(fin, bc * out, generator=gen)
+    b2 = torch.rand(1, bc * out, generator=gen)
+    y = batch_fc(x2, w2, b2, batchcount=bc)
+    for k in range(bc):
+        want = x2[:, k * fin:(k + 1) * fin] @ w2[:, k * out:(k + 1) * out] + b2[:, k * out:(k + 1) * out]
+        assert torch.allclose(y[:, k * out:(k + 1) * out], want, atol=1e-6)
+    x3 = torch.rand(bc, ins, fin, generator=gen)
+    yt = batch_fc(x3, w2, b2, batchcount=bc, transpose_weight=True, act="relu")
+    for k in range(bc):
+        want = torch.relu(x3[k] @ w2[:, k * out:(k + 1) * out] + b2[:, k * out:(k + 1) * out])
+        assert torch.allclose(yt[k], want, atol=1e-6)
+    with pytest.raises(ValueError):
+        batch_fc(x3, w2, b2, transpose_weight=True)
