@@ -271,20 +271,34 @@ def shuffle_batch(x: torch.Tensor, seed: int | None = None):
     return x[idx], idx
 
 
-def filter_by_instag(ins: torch.Tensor, ins_tag_lod, ins_tags: torch.Tensor, filter_tags, out_val_if_empty: float = 0.0):
-    """Keep the instances that carry at least one of ``filter_tags`` (reference
-    filter_by_instag_op.*): ``ins_tag_lod`` are the per-instance tag offsets into
-    ``ins_tags``.  Returns (kept rows, index map [kept, 2] = (new row, old row), loss weight)."""
+def filter_by_instag(ins: torch.Tensor, ins_tag_lod, ins_tags: torch.Tensor, filter_tags, out_val_if_empty: float = 0.0,
+                     ins_lod=None):
+    """Keep the instances that carry at least one of ``filter_tags`` (reference filter_by_instag_op.h:40-193;
+    oracle test_filter_by_instag_op.py).  ``ins_tag_lod``: per-instance tag offsets into ``ins_tags``;
+    ``ins_lod``: per-instance ROW offsets into ``ins`` (``is_lod``; default one row per instance).
+
+    Returns ``(out, index_map, loss_weight)``: ``out`` = all rows of the kept instances (differentiable),
+    ``index_map`` int64 ``[kept, 3]`` = (first output row, first input row, row count), ``loss_weight``
+    ``[kept, 1]`` ones.  With nothing kept: one row of ``out_val_if_empty``, map ``[[0, 1, 1]]``, weight 0.
+    ``out.lod`` (attribute) holds the output row offsets."""
     want = set(int(t) for t in filter_tags)
-    tags = ins_tags.tolist()
-    keep = [i for i in range(len(ins_tag_lod) - 1)
-            if any(int(t) in want for t in tags[ins_tag_lod[i]:ins_tag_lod[i + 1]])]
+    tags = ins_tags.reshape(-1).tolist()
+    n_ins = len(ins_tag_lod) - 1
+    rows_lod = list(ins_lod) if ins_lod is not None else list(range(n_ins + 1))
+    keep = [i for i in range(n_ins) if any(int(t) in want for t in tags[ins_tag_lod[i]:ins_tag_lod[i + 1]])]
     if not keep:
         out = torch.full((1, ins.shape[1]), out_val_if_empty, dtype=ins.dtype, device=ins.device)
-        return out, torch.zeros(1, 2, dtype=torch.int64), torch.zeros(1, 1, dtype=ins.dtype, device=ins.device)
-    idx = torch.tensor(keep, device=ins.device)
-    index_map = torch.stack([torch.arange(len(keep)), torch.tensor(keep)], 1)
-    return ins[idx], index_map, torch.ones(len(keep), 1, dtype=ins.dtype, device=ins.device)
+        out.lod = [0, 1]
+        return out, torch.tensor([[0, 1, 1]], dtype=torch.int64), torch.zeros(1, 1, dtype=torch.float32, device=ins.device)
+    src, imap, out_lod = [], [], [0]
+    for i in keep:
+        b, e = rows_lod[i], rows_lod[i + 1]
+        imap.append([out_lod[-1], b, e - b])
+        src.extend(range(b, e))
+        out_lod.append(out_lod[-1] + e - b)
+    out = ins[torch.tensor(src, dtype=torch.long, device=ins.device)]
+    out.lod = out_lod
+    return out, torch.tensor(imap, dtype=torch.int64), torch.ones(len(keep), 1, dtype=torch.float32, device=ins.device)
 
 
 # ---------------------------------------------------------------- fused_seqpool_cvm_with_pcoc

@@ -168,9 +168,17 @@ def test_batch_fc_scaled_fc_cross_norm_and_slices():
     sh, idx = O.shuffle_batch(a, seed=3)
     assert torch.equal(sh, a[idx]) and sorted(idx.tolist()) == [0, 1, 2]
     kept, imap, w8 = O.filter_by_instag(a, [0, 1, 3, 4], torch.tensor([5, 6, 7, 8]), [7])
-    assert torch.equal(kept, a[1:2]) and imap.tolist() == [[0, 1]]
-    none, _, lw = O.filter_by_instag(a, [0, 1, 3, 4], torch.tensor([5, 6, 7, 8]), [99])
-    assert none.shape == (1, 4) and lw.item() == 0
+    assert torch.equal(kept, a[1:2]) and imap.tolist() == [[0, 1, 1]]
+    none, nmap, lw = O.filter_by_instag(a, [0, 1, 3, 4], torch.tensor([5, 6, 7, 8]), [99])
+    assert none.shape == (1, 4) and lw.item() == 0 and nmap.tolist() == [[0, 1, 1]]
+    # the reference's first test case (test_filter_by_instag_op.py:30-72): instance i owns i+1 rows
+    x1 = torch.arange(36.)[:, None].repeat(1, 4).requires_grad_(True)
+    lod1 = [0, 1, 3, 6, 10, 15, 21, 28, 36]
+    out, mm, lw = O.filter_by_instag(x1, list(range(9)), torch.tensor([1, 2, 1, 2, 1, 2, 1, 2]), [2], ins_lod=lod1)
+    assert mm.tolist() == [[0, 1, 2], [2, 6, 4], [6, 15, 6], [12, 28, 8]] and out.lod == [0, 2, 6, 12, 20]
+    assert out[:, 0].tolist() == [1, 2, 6, 7, 8, 9] + list(range(15, 21)) + list(range(28, 36)) and lw.tolist() == [[1.]] * 4
+    out.sum().backward()
+    assert x1.grad[:, 0].tolist() == [0, 1, 1, 0, 0, 0, 1, 1, 1, 1] + [0] * 5 + [1] * 6 + [0] * 7 + [1] * 8
 
 
 def test_seqpool_autograd_wrapper_and_variants_cpu():
