@@ -302,37 +302,70 @@ def filter_by_instag(ins: torch.Tensor, ins_tag_lod, ins_tags: torch.Tensor, fil
 
 
 # ---------------------------------------------------------------- fused_seqpool_cvm_with_pcoc
+class _SeqpoolCVMWithPCOC(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, cvm, q_values, lod, B, S, use_cvm, used, mx, pad_value, need_filter, show_coeff, clk_coeff,
+                threshold, quant_ratio):
+        H = x.shape[1]
+        G = B * S
+        lens = (lod[1:] - lod[:-1]).long()
+        n = int(lod[-1])
+        seg = torch.repeat_interleave(torch.arange(G, device=x.device), lens, output_size=n)
+        rows = x[:n]
+        if need_filter:                                   # whole rows are skipped (kernel QuantFilter :87-120)
+            keep = ~((rows[:, 0] - rows[:, 1]) * show_coeff + rows[:, 1] * clk_coeff < threshold)
+            rows = rows * keep[:, None].to(x.dtype)
+        if quant_ratio > 0:                               # only the columns behind max_cvm_offset (:72-80)
+            emb = torch.trunc(rows[:, mx:] * quant_ratio + 0.5) / quant_ratio
+            rows = torch.cat([rows[:, :mx], emb], 1)
+        pooled = torch.zeros(G, H, dtype=x.dtype, device=x.device).index_add_(0, seg, rows) + pad_value
+        if use_cvm:
+            pn = used - 4                                 # show, clk, show2, clk2, then pclk_0..pclk_{pn-1}
+            lg = torch.log(pooled[:, :used] + 1)
+            cols = [lg[:, 0:1], lg[:, 1:2] - lg[:, 0:1], lg[:, 4:4 + pn] - lg[:, 2:3], lg[:, 4:4 + pn] - lg[:, 3:4],
+                    pooled[:, mx:]]
+            out = torch.cat(cols, 1)
+        else:
+            out = pooled[:, mx:]
+        ctx.meta = (B, S, H, n, use_cvm, used, mx, out.shape[1])
+        ctx.save_for_backward(cvm, q_values, seg)
+        E = out.shape[1]
+        return out.view(S, B, E).permute(1, 0, 2).reshape(B, S * E)
+
+    @staticmethod
+    def backward(ctx, dout):
+        cvm, q_values, seg = ctx.saved_tensors
+        B, S, H, n, use_cvm, used, mx, E = ctx.meta
+        b_of = seg % B
+        dx = torch.zeros(n, H, dtype=dout.dtype, device=dout.device)
+        dx[:, :4] = cvm[b_of, :4]                         # show / clk / show2 / clk2 counts ride on the gradient
+        if used > 4 and q_values is not None:
+            dx[:, 4:used] = q_values.reshape(B, used - 4)[b_of]
+        d = dout.reshape(B, S, E)[b_of, seg // B]
+        dx[:, mx:] = d[:, E - (H - mx):]
+        return (dx,) + (None,) * 14
+
+
 def fused_seqpool_cvm_with_pcoc(x: torch.Tensor, lod: torch.Tensor, batch_size: int, num_slots: int,
-                                pcoc_cvm: torch.Tensor | None = None, use_cvm: bool = True, cvm_offset: int = 7,
+                                cvm: torch.Tensor | None = None, q_values: torch.Tensor | None = None,
+                                use_cvm: bool = True, cvm_offset: int = 7, max_cvm_offset: int | None = None,
                                 pad_value: float = 0.0, need_filter: bool = False, show_coeff: float = 0.2,
                                 clk_coeff: float = 1.0, threshold: float = 0.96, quant_ratio: int = 0):
-    """PCOC variant: the value rows carry ``cvm_offset`` leading statistics columns — show,
-    click and ``pclk_num = (cvm_offset - 2)`` predicted-click sums; output cvm columns are
-    ``log(show+1), log(clk+1)-log(show+1)`` followed by
-    ``log(pclk_i+1) - log(show+1)`` ... calibrated per q-value bucket
-    (reference fused_seqpool_cvm_with_pcoc_op.cu:36-294).  Sum-pooling via segment sums."""
-    H = x.shape[1]
-    G = batch_size * num_slots
-    lens = (lod[1:] - lod[:-1]).long()
-    seg = torch.repeat_interleave(torch.arange(G, device=x.device), lens)
-    rows = x
-    if need_filter:
-        sc = (x[:, 0] - x[:, 1]) * show_coeff + x[:, 1] * clk_coeff
-        keep = ~(sc < threshold)
-        rows = x * keep[:, None].to(x.dtype)
-    emb = rows[:, cvm_offset:]
-    if quant_ratio > 0:
-        emb = torch.trunc(emb * quant_ratio + 0.5) / quant_ratio
-        rows = torch.cat([rows[:, :cvm_offset], emb], 1)
-    pooled = torch.zeros(G, H, dtype=x.dtype, device=x.device).index_add_(0, seg, rows) + pad_value
-    if use_cvm:
-        show = torch.log(pooled[:, 0:1] + 1)
-        stats = torch.log(pooled[:, 1:cvm_offset] + 1) - show
-        out = torch.cat([show, stats, pooled[:, cvm_offset:]], 1)
-    else:
-        out = pooled[:, cvm_offset:]
-    E = out.shape[1]
-    return out.view(num_slots, batch_size, E).permute(1, 0, 2).reshape(batch_size, num_slots * E)
+    """PCOC variant (fused_seqpool_cvm_with_pcoc_op.cu:36-330).  Value rows ``[N, H]`` carry
+    ``max_cvm_offset`` statistics columns — ``show, clk, show2, clk2, pclk_0 .. pclk_{n-1}`` with
+    ``n = cvm_offset - 4`` (``cvm_offset`` = the op's ``used`` offset; columns ``cvm_offset .. max`` are
+    unused) — then the embedding.  Output per (slot, instance), ``use_cvm``:
+    ``[log(show+1), log(clk+1)-log(show+1), log(pclk_j+1)-log(show2+1) (n cols), log(pclk_j+1)-log(clk2+1)
+    (n cols), embedding...]``; otherwise the embedding only.  Backward writes into every pooled row:
+    columns 0-3 from ``cvm`` ``[B, >=4]``, the pclk columns from ``q_values`` ``[B, n]`` (the stored q-values of
+    the instances, ``store_q_value``), and the output gradient behind ``max_cvm_offset``."""
+    mx = cvm_offset if max_cvm_offset is None else max_cvm_offset
+    if cvm_offset < 4 or mx < cvm_offset:
+        raise ValueError("with_pcoc needs cvm_offset >= 4 (show, clk, show2, clk2) and max_cvm_offset >= cvm_offset")
+    if cvm is None:
+        cvm = torch.zeros(batch_size, 4, dtype=x.dtype, device=x.device)
+    return _SeqpoolCVMWithPCOC.apply(x, cvm, q_values, lod, batch_size, num_slots, use_cvm, cvm_offset, mx, pad_value,
+                                     need_filter, show_coeff, clk_coeff, threshold, quant_ratio)
 
 
 def cross_norm_layer_hadamard(fields_num: int, embed_dim: int, **kw) -> CrossNormHadamard:

@@ -197,8 +197,26 @@ def test_seqpool_autograd_wrapper_and_variants_cpu():
     assert torch.all(g[:, 2:] == 1)
     b_of_k = torch.repeat_interleave(torch.arange(S * B) % B, lens)
     assert torch.allclose(g[:, :2], cvm[b_of_k])
-    pc = O.fused_seqpool_cvm_with_pcoc(x.detach(), lod, B, S, cvm_offset=4)
-    assert pc.shape == (B, S * H)
+    # PCOC: 7 statistics columns (show, clk, show2, clk2, 2 pclk, 1 unused), checked bag by bag
+    H2, used, mx = 7 + 3, 6, 7
+    xp = (torch.rand(int(lod[-1]), H2, generator=gen) * 3).requires_grad_(True)
+    cvm4, qv = torch.rand(B, 4, generator=gen), torch.rand(B, 2, generator=gen)
+    pc = O.fused_seqpool_cvm_with_pcoc(xp, lod, B, S, cvm=cvm4, q_values=qv, cvm_offset=used, max_cvm_offset=mx)
+    Eo = 2 + 2 * 2 + 3
+    assert pc.shape == (B, S * Eo)
+    ll = lod.tolist()
+    for s_ in range(S):
+        for b_ in range(B):
+            p_ = xp.detach()[ll[s_ * B + b_]:ll[s_ * B + b_ + 1]].sum(0)
+            lg = torch.log(p_ + 1)
+            want = torch.cat([lg[0:1], lg[1:2] - lg[0:1], lg[4:6] - lg[2], lg[4:6] - lg[3], p_[7:]])
+            assert torch.allclose(pc[b_, s_ * Eo:(s_ + 1) * Eo], want, atol=1e-5)
+    pc.sum().backward()
+    gp = xp.grad
+    assert torch.allclose(gp[:, :4], cvm4[b_of_k]) and torch.allclose(gp[:, 4:6], qv[b_of_k])
+    assert torch.all(gp[:, 6] == 0) and torch.all(gp[:, 7:] == 1)
+    nocvm = O.fused_seqpool_cvm_with_pcoc(xp.detach(), lod, B, S, use_cvm=False, cvm_offset=used, max_cvm_offset=mx)
+    assert nocvm.shape == (B, S * 3)
 
 
 def test_side_tables_and_file_mgr(tmp_path):
