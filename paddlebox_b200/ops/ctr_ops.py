@@ -113,38 +113,76 @@ def batch_fc(x: torch.Tensor, w: torch.Tensor, b: torch.Tensor, act: str | None 
 
 # ---------------------------------------------------------------- scaled_fc
 def scaled_fc(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, input_scale_factor: float = 1.0,
-              bias_scale_factor: float = 1.0, grad_scale_factor: float = 1.0) -> torch.Tensor:
-    """fp16 GEMM with scaled input and bias: ``(x*s_in) @ w + bias*s_b`` computed in half
-    precision, result cast back to fp32 (reference scaled_fc_op.cu:39-342).  Here the operands
-    are rounded to bf16 and accumulated in fp32 — the tcgen05 kernel's native mode."""
+              bias_scale_factor: float = 1.0, grad_scale_factor: float = 256.0) -> torch.Tensor:
+    """Half-precision FC with range scaling (reference scaled_fc_op.cu:39-342).  The scales exist only to keep
+    the half-precision intermediates in range; net of them the op computes
+
+        out = x @ w + bias * (bias_scale_factor / input_scale_factor)      (inf -> nan on the way out)
+        dx  = dout @ w^T,   dw = x^T @ dout,   db = column sums of dout    (unscaled, as the reference)
+
+    with every GEMM operand rounded to 16 bits: the forward product is formed as
+    ``input_scale * (x16 @ w16) + bias16 * bias_scale`` and divided by ``input_scale``; the backward operand
+    is ``dout * grad_scale / input_scale`` and the results are divided by ``grad_scale``.  The reference rounds
+    to fp16; here to bf16, the tcgen05 kernel's operand type (fp32 accumulate)."""
+    s_in, s_b, s_g = float(input_scale_factor), float(bias_scale_factor), float(grad_scale_factor)
+
+    def r16(t):
+        return t.to(torch.bfloat16).float()
+
     class _Fn(torch.autograd.Function):
         @staticmethod
         def forward(ctx, x, w, bias):
             ctx.save_for_backward(x, w)
-            xs = (x * input_scale_factor).to(torch.bfloat16).float()
-            ws = w.to(torch.bfloat16).float()
-            return xs @ ws + bias * bias_scale_factor
+            y = (s_in * (r16(x) @ r16(w)) + r16(bias) * s_b) / s_in
+            return torch.where(torch.isinf(y), torch.full_like(y, float("nan")), y)
 
         @staticmethod
         def backward(ctx, g):
             x, w = ctx.saved_tensors
-            g = g * grad_scale_factor
-            gb = g.to(torch.bfloat16).float()
-            dx = (gb @ w.to(torch.bfloat16).float().t()) * input_scale_factor / grad_scale_factor
-            dw = ((x * input_scale_factor).to(torch.bfloat16).float().t() @ gb) / grad_scale_factor
-            db = g.sum(0) * bias_scale_factor / grad_scale_factor
-            return dx, dw, db
+            g16 = r16(g * (s_g / s_in))
+            dx = s_in * (g16 @ r16(w).t()) / s_g
+            dw = s_in * (r16(x).t() @ g16) / s_g
+            return dx, dw, g.sum(0)
     return _Fn.apply(x, w, bias)
 
 
-def scaled_int8fc(x, w, bias, input_scale_factor=1.0, bias_scale_factor=1.0, weight_scale: float = 127.0):
-    """int8-weight variant (reference scaled_int8fc_op.cu:38-440): weights are quantised to
-    int8 with a symmetric scale, the product is de-quantised.  B200 tensor cores still have an
-    int8 path, but the CTR towers here keep bf16; this op simulates the quantisation."""
-    wmax = w.detach().abs().amax().clamp(min=1e-8)
-    wq = torch.round(w / wmax * weight_scale).clamp(-127, 127)
-    wdq = (wq * wmax / weight_scale).detach() + (w - w.detach())     # straight-through estimator
-    return (x * input_scale_factor) @ wdq + bias * bias_scale_factor
+def _int8_quant(v: torch.Tensor, expand: float, clip: float, int8_range: float) -> torch.Tensor:
+    """``int8(clamp(v * expand, -clip, clip) / interval + 0.5)`` with ``interval = 2 * clip / int8_range`` and
+    the C cast's truncation toward zero (scaled_int8fc_op.cu:38-72)."""
+    interval = 2.0 * clip / int8_range
+    return torch.trunc((v * expand).clamp(-clip, clip) / interval + 0.5).clamp(-128, 127)
+
+
+def scaled_int8fc(x, w, bias, input_scale_factor=1.0, bias_scale_factor=1.0, grad_scale_factor=1.0,
+                  input_expand_factor: float = 1.0, input_clip_factor: float = 2.0, weight_expand_factor: float = 1.0,
+                  weight_clip_factor: float = 2.0, int8_range: float = 240.0, dequant_weights: bool = False):
+    """int8 FC (reference scaled_int8fc_op.cu:38-440): input and weight are expanded, clipped and quantised
+    to int8, multiplied with integer accumulation, and the product is scaled back by
+    ``input_interval / (input_expand * weight_expand)`` before the (unscaled) bias is added.  The reference
+    leaves the WEIGHT interval out of that rescale (its two-interval line is commented out), so with the
+    default clip / range the output is ``1 / weight_interval`` times the real product; ``dequant_weights=True``
+    applies both intervals instead.  Backward is the plain fp32 FC gradient (straight-through), as in the
+    reference (:405-430).  B200 keeps an int8 tensor-core path, but the towers here run bf16: the integer
+    product is formed in fp32, which is exact for these magnitudes."""
+    in_int = 2.0 * input_clip_factor / int8_range
+    w_int = 2.0 * weight_clip_factor / int8_range
+
+    class _Fn(torch.autograd.Function):
+        @staticmethod
+        def forward(ctx, x, w, bias):
+            ctx.save_for_backward(x, w)
+            xq = _int8_quant(x, input_expand_factor, input_clip_factor, int8_range)
+            wq = _int8_quant(w, weight_expand_factor, weight_clip_factor, int8_range)
+            y = (xq @ wq) / (input_expand_factor * weight_expand_factor) * in_int
+            if dequant_weights:
+                y = y * w_int
+            return y + bias
+
+        @staticmethod
+        def backward(ctx, g):
+            x, w = ctx.saved_tensors
+            return g @ w.t(), x.t() @ g, g.sum(0)
+    return _Fn.apply(x, w, bias)
 
 
 # ---------------------------------------------------------------- cross_norm_hadamard

@@ -150,10 +150,23 @@ def test_batch_fc_scaled_fc_cross_norm_and_slices():
     assert O.BatchFC(4, 5, 3)(x).shape == torch.Size([4, 6, 3])
     xi, wi, bi = torch.randn(8, 16, requires_grad=True), torch.randn(16, 4, requires_grad=True), torch.randn(4)
     y = O.scaled_fc(xi, wi, bi, input_scale_factor=2.0, bias_scale_factor=0.5)
-    assert torch.allclose(y, (2 * xi) @ wi + 0.5 * bi, rtol=3e-2, atol=3e-2)
+    assert torch.allclose(y, xi @ wi + 0.25 * bi, rtol=3e-2, atol=6e-2)        # scales cancel but for bias_scale / input_scale
     y.sum().backward()
-    assert torch.allclose(xi.grad, (torch.ones(8, 4) @ wi.t()) * 2, rtol=3e-2, atol=3e-2)
-    assert O.scaled_int8fc(xi.detach(), wi.detach(), bi).shape == (8, 4)
+    assert torch.allclose(xi.grad, torch.ones(8, 4) @ wi.t(), rtol=3e-2, atol=3e-2)
+    assert torch.allclose(wi.grad, xi.detach().t() @ torch.ones(8, 4), rtol=3e-2, atol=6e-2)
+    assert torch.isnan(O.scaled_fc(torch.full((1, 2), 3e38), torch.full((2, 1), 3e38), torch.zeros(1))).all()
+    # int8: integer product of the quantised operands, rescaled by the INPUT interval only (reference quirk)
+    xq, wq = torch.tensor([[0.5, -0.7, 3.0]]), torch.tensor([[1.0], [0.25], [-2.5]])
+    q = lambda v: torch.trunc(v.clamp(-2, 2) * 60 + 0.5)
+    assert q(xq).tolist() == [[30.0, -41.0, 120.0]] and q(wq).reshape(-1).tolist() == [60.0, 15.0, -119.0]   # -119.5 truncates toward zero
+    want = (q(xq) @ q(wq)) / 60.0 + 1.0
+    got8 = O.scaled_int8fc(xq, wq, torch.ones(1))
+    assert torch.allclose(got8, want)
+    real = O.scaled_int8fc(xq, wq, torch.ones(1), dequant_weights=True)
+    assert torch.allclose(real, xq.clamp(-2, 2) @ wq.clamp(-2, 2) + 1.0, atol=0.05)
+    xg = xq.clone().requires_grad_(True)
+    O.scaled_int8fc(xg, wq, torch.ones(1)).sum().backward()
+    assert torch.equal(xg.grad, wq.t())
     cn = O.CrossNormHadamard(fields_num=2, embed_dim=3)
     xin = torch.rand(5, 12)
     out = cn(xin)
