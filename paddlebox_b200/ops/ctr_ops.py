@@ -222,16 +222,28 @@ def fused_concat(inputs, start_index: int = 0, length: int = -1, axis: int = 1) 
     return torch.cat(outs, dim=axis)
 
 
+def _partial_range(width: int, start_index: int, length: int):
+    """Column range of the partial ops: a negative start counts from the end, a negative length means "to
+    the end" (np oracle, test_partial_concat_op.py:25-40)."""
+    if not -width <= start_index < width:
+        raise ValueError(f"start_index {start_index} out of range for {width} columns")
+    s = start_index + width if start_index < 0 else start_index
+    n = width - s if length < 0 else length
+    if s + n > width:
+        raise ValueError(f"columns [{s}, {s + n}) exceed the input width {width}")
+    return s, s + n
+
+
 def partial_concat(inputs, start_index: int = 0, length: int = -1) -> torch.Tensor:
-    """reference partial_concat op (operators/partial_concat_op.*)."""
-    return fused_concat(inputs, start_index, length, 1)
+    """The same column slice of every input, side by side (operators/partial_concat_op.*)."""
+    b, e = _partial_range(inputs[0].shape[1], start_index, length)
+    return torch.cat([t[:, b:e] for t in inputs], 1)
 
 
 def partial_sum(inputs, start_index: int = 0, length: int = -1) -> torch.Tensor:
     """Sum of the same column slice of every input (operators/partial_sum_op.*)."""
-    s = start_index
-    outs = [t[:, s:(t.shape[1] if length < 0 else s + length)] for t in inputs]
-    return torch.stack(outs, 0).sum(0)
+    b, e = _partial_range(inputs[0].shape[1], start_index, length)
+    return torch.stack([t[:, b:e] for t in inputs], 0).sum(0)
 
 
 def fused_seqpool_concat(inputs, num_slots: int, offsets=None, dims=None, lod: torch.Tensor | None = None,

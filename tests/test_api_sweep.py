@@ -354,3 +354,15 @@ def test_batch_fc_layouts():
         assert torch.allclose(yt[k], want, atol=1e-6)
     with pytest.raises(ValueError):
         batch_fc(x3, w2, b2, transpose_weight=True)
+
+
+def test_partial_ops_ranges():
+    from paddlebox_b200.ops.ctr_ops import fused_concat, partial_concat, partial_sum
+    a, b = torch.arange(12.).reshape(3, 4), torch.arange(12., 24.).reshape(3, 4)
+    assert torch.equal(partial_concat([a, b], -3, 2), torch.cat([a[:, 1:3], b[:, 1:3]], 1))
+    assert torch.equal(partial_concat([a, b], 2), torch.cat([a[:, 2:], b[:, 2:]], 1))
+    assert torch.equal(partial_sum([a, b], -1), a[:, 3:] + b[:, 3:])
+    for bad in ((4, 1), (-5, 1), (2, 3)):
+        with pytest.raises(ValueError):
+            partial_concat([a, b], *bad)
+    assert torch.equal(fused_concat([a, b], -2, 2), torch.cat([a[:, :2], b[:, :2]], 1))     # fused_concat clamps to 0
