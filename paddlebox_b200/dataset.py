@@ -749,8 +749,9 @@ class _BatchLoader:
         sid, rk, cm = self.native.batch_meta(self.worker, b, B)
         sid_t = torch.from_numpy(sid.astype(np.int64))
         rk_t = torch.from_numpy(rk.astype(np.int32))
-        return {"search_id": sid_t, "rank": rk_t, "cmatch": torch.from_numpy(cm.astype(np.int32)),
-                "rank_offset": build_rank_offset(sid_t, rk_t, self.max_rank)}
+        cm_t = torch.from_numpy(cm.astype(np.int32))
+        return {"search_id": sid_t, "rank": rk_t, "cmatch": cm_t,
+                "rank_offset": build_rank_offset(sid_t, rk_t, self.max_rank, cmatch=cm_t)}
 
     def _split(self, ids):
         if self.with_meta:

@@ -42,10 +42,12 @@ def rank_attention2(x, rank_offset, rank_param, max_rank: int = 3):
     return rank_attention(x, rank_offset, rank_param, max_rank)
 
 
-def build_rank_offset(search_id: torch.Tensor, rank: torch.Tensor, max_rank: int = 3) -> torch.Tensor:
+def build_rank_offset(search_id: torch.Tensor, rank: torch.Tensor, max_rank: int = 3,
+                      cmatch: torch.Tensor | None = None, valid_cmatch=(222, 223)) -> torch.Tensor:
     """Rank-offset matrix of a PV-merged batch (reference CopyRankOffsetKernel /
     GetRankOffset, data_feed.cu:1319-1369, data_feed.cc:3531-3591): rows of one ``search_id``
-    are one page view; ranks are 1-based, ranks > max_rank are ignored."""
+    are one page view; ranks are 1-based, ranks > max_rank are ignored.  With ``cmatch`` given, only ads
+    whose cmatch is 222 or 223 take part (data_feed.cc:3557-3560), the others get rank -1."""
     n = search_id.numel()
     out = torch.full((n, 2 * max_rank + 1), -1, dtype=torch.int32)
     if n == 0:
@@ -53,6 +55,12 @@ def build_rank_offset(search_id: torch.Tensor, rank: torch.Tensor, max_rank: int
     sid = search_id.reshape(-1).cpu()
     rk = rank.reshape(-1).cpu().long()
     valid = (rk >= 1) & (rk <= max_rank)
+    if cmatch is not None:
+        cm = cmatch.reshape(-1).cpu().long()
+        ok = torch.zeros_like(valid)
+        for c in valid_cmatch:
+            ok |= cm == c
+        valid &= ok
     out[valid, 0] = rk[valid].int()
     _, inv = torch.unique(sid, return_inverse=True)
     rows = torch.arange(n)

@@ -450,6 +450,9 @@ def test_pv_batches_carry_rank_offset(tmp_path):
     # ranks outside [1, max_rank] are ignored
     ro = build_rank_offset(torch.tensor([5, 5, 5]), torch.tensor([1, 9, 2]), 3)
     assert ro[1].tolist() == [-1] * 7 and ro[0].tolist() == [1, 1, 0, 2, 2, -1, -1]
+    # only cmatch 222 / 223 ads take part when cmatch is given (data_feed.cc:3557-3560)
+    ro = build_rank_offset(torch.tensor([5, 5, 5]), torch.tensor([1, 2, 3]), 3, cmatch=torch.tensor([222, 100, 223]))
+    assert ro[1].tolist() == [-1] * 7 and ro[0].tolist() == [1, 1, 0, -1, -1, 3, 2] and ro[2, 0] == 3
 
 
 def test_merge_by_ins_id(tmp_path):
