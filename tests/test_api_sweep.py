@@ -366,3 +366,43 @@ def test_partial_ops_ranges():
         with pytest.raises(ValueError):
             partial_concat([a, b], *bad)
     assert torch.equal(fused_concat([a, b], -2, 2), torch.cat([a[:, :2], b[:, :2]], 1))     # fused_concat clamps to 0
+
+
+def test_dataset_edge_cases_do_not_crash(tmp_path):
+    from paddlebox_b200 import _native as N
+    ds = DatasetFactory().create_dataset("InMemoryDataset")
+    ds.set_use_var(slot_vars(2, 1))
+    ds.set_batch_size(4)
+    ds.set_thread(2)
+    # no files at all, then an empty file: an empty pass, no batches, nothing to save
+    ds.set_filelist([])
+    ds.load_into_memory()
+    assert ds.get_memory_data_size() == 0
+    (tmp_path / "empty").write_text("")
+    ds.set_filelist([str(tmp_path / "empty")])
+    ds.load_into_memory()
+    ds.prepare_train(2)
+    assert ds.get_memory_data_size() == 0 and list(ds.batches(worker=0)) == [] and list(ds.batches(worker=1)) == []
+    with pytest.raises(N.NativeError):
+        ds.save_pass_file(str(tmp_path / "none.arena"))
+    # a missing file is an error, not a crash; the dataset stays usable
+    ds.set_filelist([str(tmp_path / "missing")])
+    with pytest.raises(N.NativeError):
+        ds.load_into_memory()
+    # malformed lines are counted and skipped; fewer instances than workers gives zero batches
+    (tmp_path / "mixed").write_text("1 1.0 1 0.5 1 7 1 8\nnot a line\n1 0 1 0.5 0 1 9\n1 1.0 1 0.25 2 3 4 1 5\n\n")
+    ds.set_filelist([str(tmp_path / "mixed")])
+    ds.load_into_memory()
+    assert ds.get_memory_data_size() == 2 and "bad_lines=3" in ds.stats()
+    ds.prepare_train(4)
+    assert all(list(ds.batches(worker=w)) == [] for w in range(4))
+    ds.prepare_train(1, 0, shuffle=False)
+    (b,) = list(ds.batches(worker=0))
+    assert b.batch_size == 2 and sorted(b.keys.tolist()) == [3, 4, 5, 7, 8]
+    with pytest.raises(N.NativeError):
+        ds._native.pack_batch(0, 5, 0, 0, 0, False)            # batch index out of range
+    # a pass file that is not one
+    (tmp_path / "junk.arena").write_bytes(b"x" * 300)
+    with pytest.raises(N.NativeError, match="pass file"):
+        ds.load_pass_file(str(tmp_path / "junk.arena"))
+    assert ds.get_memory_data_size() == 0                      # the previous pass was released first
