@@ -406,3 +406,42 @@ def test_dataset_edge_cases_do_not_crash(tmp_path):
     with pytest.raises(N.NativeError, match="pass file"):
         ds.load_pass_file(str(tmp_path / "junk.arena"))
     assert ds.get_memory_data_size() == 0                      # the previous pass was released first
+
+
+def test_host_table_and_metric_edge_cases(tmp_path):
+    from paddlebox_b200 import _native as N
+    from paddlebox_b200.host import HostAuc, HostTable, sort_unique_u64, partition_by_owner
+    t = HostTable(4)
+    empty = np.zeros(0, np.uint64)
+    assert t.fetch_rows(empty).shape == (0, t.layout.stride) and t.pull(empty).shape == (0, 7)
+    t.push(empty, np.zeros((0, t.layout.push_stride), np.float32))
+    assert t.size() == 0 and t.save(str(tmp_path / "m")) == 0 and t.shrink() == 0 and t.keys().size == 0
+    # key 0 is the padding key: pulls zeros, pushes are ignored
+    t.fetch_rows(np.array([0, 5], np.uint64))
+    p = np.zeros((2, t.layout.push_stride), np.float32)
+    p[:, 1] = 1
+    t.push(np.array([0, 5], np.uint64), p)
+    rows = t.fetch_rows(np.array([0, 5], np.uint64), create=False)
+    assert rows[0, 0] == 0 and rows[1, 0] == 1 and torch.all(t.pull(np.array([0], np.uint64)) == 0)
+    # unknown keys pull zeros and are not created; a push to an unknown key is dropped
+    assert torch.all(t.pull(np.array([77], np.uint64)) == 0) and t.size() == 2
+    t.push(np.array([77], np.uint64), p[:1])
+    assert t.size() == 2
+    # malformed checkpoint lines are skipped
+    d = tmp_path / "ck"
+    d.mkdir()
+    (d / "part-000-00000").write_text("garbage\n12 0 0 3 1 0.5 0 2 0\n13 1\n\n")
+    t2 = HostTable(4)
+    assert t2.load(str(d)) == 1 and t2.keys().tolist() == [12]
+    with pytest.raises((N.NativeError, OSError)):
+        t2.save("/proc/definitely/not/writable")
+    assert sort_unique_u64(empty).size == 0 and [x.size for x in partition_by_owner(empty, 3)] == [0, 0, 0]
+    # metrics with no data, one class only, NaN predictions
+    a = HostAuc(1000)
+    out = a.compute()
+    assert len(out) == 8 and out[7] == 0 and all(np.isfinite(out))
+    a.add(np.array([0.2, 0.8], np.float32), np.array([1.0, 1.0], np.float32))
+    out = a.compute()
+    assert out[7] == 2 and np.isfinite(out[0])
+    a.add(np.array([np.nan, np.inf], np.float32), np.array([0.0, 1.0], np.float32))
+    assert a.nan_inf() == (1, 1)
