@@ -386,6 +386,7 @@ bool Dataset::parse_line(const char* line, size_t len, SlotRecord* rec) const {
     if (parse_logkey) {
       if (!read_u64(p, e, &n) || n != 1 || !read_token(p, e, &tb, &tl)) return false;
       // logkey hex layout: [11,14) cmatch, [14,16) rank, [16,32) search_id (data_feed.cc:2385-2396)
+      rec->ins_id.assign(tb, tl);         // the logkey becomes the instance id (data_feed.cc:4071)
       if (tl >= 32) {
         std::string lk(tb, tl);
         rec->search_id = strtoull(lk.substr(16, 16).c_str(), nullptr, 16);
