@@ -445,3 +445,26 @@ def test_host_table_and_metric_edge_cases(tmp_path):
     assert out[7] == 2 and np.isfinite(out[0])
     a.add(np.array([np.nan, np.inf], np.float32), np.array([0.0, 1.0], np.float32))
     assert a.nan_inf() == (1, 1)
+
+
+def test_numeric_gradient_checks_of_composed_ops():
+    """The reference's OpTest harness checks analytic against numeric gradients; same here in float64."""
+    from torch.autograd import gradcheck
+    from paddlebox_b200.ops import ctr_ops as CO
+    gen = torch.Generator().manual_seed(0)
+
+    def rnd(*shape):
+        return torch.rand(*shape, generator=gen, dtype=torch.float64, requires_grad=True)
+
+    ro = CO.build_rank_offset(torch.tensor([1, 1, 1, 2, 2]), torch.tensor([1, 2, 3, 2, 1]), 3)
+    assert gradcheck(lambda x, p: CO.rank_attention(x, ro, p, 3), (rnd(5, 4), rnd(9 * 4, 3)))
+    assert gradcheck(lambda x, w, b: CO.batch_fc(x, w, b), (rnd(3, 4, 5), rnd(3, 5, 2), rnd(3, 2)))
+    assert gradcheck(lambda x, w, b: CO.batch_fc(x, w, b, batchcount=3), (rnd(4, 6), rnd(2, 9), rnd(1, 9)))
+    assert gradcheck(lambda a, b: CO.partial_sum([a, b], 1, 2), (rnd(3, 4), rnd(3, 4)))
+    assert gradcheck(lambda a, b: CO.partial_concat([a, b], -2), (rnd(3, 4), rnd(3, 4)))
+    lod = torch.tensor([0, 2, 2, 3, 5, 6, 6], dtype=torch.int32)         # S = 2, B = 3
+    assert gradcheck(lambda a, b: CO.fused_seqpool_concat([a, b], 2, [1, 0], [2, 2], lod=lod, batch_size=3),
+                     (rnd(6, 4), rnd(6, 3)))
+    assert gradcheck(lambda x, ad: CO.fused_seq_tensor(x, ad, 2, 3, 3, 2, 1, 1)[0], (rnd(2, 2 * 3 * 3 * 2), rnd(2, 2 * 1 * 2)))
+    assert gradcheck(lambda x: CO.filter_by_instag(x, [0, 1, 2, 3], torch.tensor([1, 2, 1]), [1])[0], (rnd(3, 4),))
+    assert gradcheck(lambda a: CO.fused_concat([a, a * 2], 1, 2), (rnd(3, 4),))
