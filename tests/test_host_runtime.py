@@ -599,3 +599,14 @@ def test_pass_file_roundtrip_is_batch_identical(tmp_path):
     b.load_into_memory()
     assert b.get_memory_data_size() == 300
     b.release_memory()
+
+
+def test_native_util_selftest(tmp_path):
+    """C++-level test of the blocking channel and the thread pool (the reference tests these with gtests)."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    exe = tmp_path / "util_selftest"
+    subprocess.check_call(["g++", "-std=c++17", "-O1", "-pthread", "-o", str(exe),
+                           os.path.join(root, "csrc", "host", "tests", "util_selftest.cc")])
+    r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0 and "util selftest ok" in r.stdout, r.stdout + r.stderr
