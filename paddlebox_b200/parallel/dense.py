@@ -296,4 +296,9 @@ class DenseSync:
         elif self.mode == "async":
             self.async_table.wait()
             self.async_table.pull(out=self.store.flat)
+            if self.store.nranks > 1:
+                # one process per GPU means one host table per rank (the reference shares one between the
+                # GPU threads of its single process): the replicas are averaged at the end of every pass
+                self.store.average_params(False)
+                self.async_table.set_params(self.store.flat)
             self.store.mark_dirty()

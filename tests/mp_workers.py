@@ -74,6 +74,16 @@ def cpu_feed_pass_and_dense(rank, world):
     sync3.after_backward()
     dist.all_gather(gathered, store.flat)
     assert all(torch.allclose(gathered[0], t) for t in gathered)
+    # async dense mode: one host table per rank, replicas meet again at the end of the pass
+    store.gflat.zero_()
+    sync4 = DenseSync(store, DenseOptimizer(store, lr=0.01, kind="adam"), "async")
+    for _ in range(3):
+        sync4.before_forward()
+        model(torch.randn(4, 8) * (rank + 1)).sum().backward()
+        sync4.after_backward()
+    sync4.finalize()
+    dist.all_gather(gathered, store.flat)
+    assert all(torch.allclose(gathered[0], t, atol=1e-6) for t in gathered)
     # metric reduction: global AUC over both ranks' data
     m = create_metric("AucCalculator", name="a", bucket_size=10000)
     rs = np.random.RandomState(rank)
