@@ -539,7 +539,9 @@ class HostTable {
 
   // loads files written by save() with mode 0/3 (full state); serving-format files restore
   // weights with fresh optimizer state.
-  int load_file(const std::string& path, bool serving, int64_t* n_loaded) {
+  // rank / world (world > 1): only the keys this rank owns are kept — a model saved by N ranks can be
+  // loaded by M (owner = pbx_owner_of, the function that shards the table)
+  int load_file(const std::string& path, bool serving, int64_t* n_loaded, int rank = 0, int world = 1) {
     FILE* fp = fopen(path.c_str(), "r");
     PBH_REQUIRE(fp != nullptr, "cannot open %s", path.c_str());
     char* line = nullptr;
@@ -560,6 +562,7 @@ class HostTable {
       }
       size_t need = 5 + (serving ? 0 : L.embed_state) + 2;
       if (f.size() < need) continue;
+      if (world > 1 && (int)((mix64(key) >> 40) % (uint64_t)world) != rank) continue;
       float* row = find_or_create(key, true);
       init_row(row, key);
       size_t q = 0;
@@ -700,6 +703,9 @@ int pbh_table_save(void* h, const char* dir, int mode, int part_shard_base, floa
 }
 int pbh_table_load_file(void* h, const char* path, int serving, int64_t* n_loaded) {
   return ((HostTable*)h)->load_file(path, serving != 0, n_loaded);
+}
+int pbh_table_load_file_owned(void* h, const char* path, int serving, int rank, int world, int64_t* n_loaded) {
+  return ((HostTable*)h)->load_file(path, serving != 0, n_loaded, rank, world);
 }
 int pbh_table_ssd_open(void* h, const char* dir) { return ((HostTable*)h)->ssd_open(dir); }
 int pbh_table_ssd_close(void* h, int unlink_files) { ((HostTable*)h)->ssd_close(unlink_files != 0); return 0; }

@@ -91,6 +91,8 @@ int64_t pbh_table_shrink(void* t, float decay, float delete_threshold, float del
 int pbh_table_save(void* t, const char* dir, int mode, int part_shard_base, float base_threshold,
                    float delta_threshold, int clear_dirty, int64_t* n_saved);
 int pbh_table_load_file(void* t, const char* path, int serving, int64_t* n_loaded);
+/* same, keeping only the keys rank `rank` of `world` owns: a model saved by N ranks loads into M */
+int pbh_table_load_file_owned(void* t, const char* path, int serving, int rank, int world, int64_t* n_loaded);
 int64_t pbh_table_keys(void* t, uint64_t* out, int64_t max_n);
 
 /* parallel sort + unique of keys in place (end of a feed pass: PSGPUWrapper::PreBuildTask,

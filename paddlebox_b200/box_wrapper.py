@@ -327,7 +327,9 @@ class BoxWrapper:
         return f"xbox_delta={n}"
 
     def load_model(self, path: str, serving: bool = False) -> int:
-        return self.host_table.load(path, serving=serving)
+        """Load a saved model into the host tier.  With several ranks every rank reads all part files and
+        keeps the keys it owns, so the number of ranks may differ from the run that saved it."""
+        return self.host_table.load(path, serving=serving, rank=self.rank, world=self.world_size)
 
     def load_ssd2mem(self, date: str = "") -> int:
         """Bring every row of the SSD tier back into host memory (``LoadSSD2Mem(day)``,
@@ -349,7 +351,7 @@ class BoxWrapper:
     def merge_model(self, path: str) -> int:
         """Merge another checkpoint into the host tier (``MergeModel``): loaded rows replace
         existing ones."""
-        return self.host_table.load(path)
+        return self.host_table.load(path, rank=self.rank, world=self.world_size)
 
     def merge_multi_models(self, paths, update_type: int = 0, idx: int = 0) -> int:
         """``MergeMultiModels(path, update_type, idx)``: merge several checkpoints into the host
@@ -367,7 +369,7 @@ class BoxWrapper:
                 if len(keys):
                     rows = self.host_table.fetch_rows(keys, create=False)
                     acc = {int(k): (float(r[0]), float(r[1])) for k, r in zip(keys, rows)}
-            n += self.host_table.load(p)
+            n += self.host_table.load(p, rank=self.rank, world=self.world_size)
             if update_type == 1 and acc:
                 keys = self.host_table.keys()
                 rows = self.host_table.fetch_rows(keys, create=False).copy()

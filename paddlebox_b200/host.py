@@ -112,14 +112,16 @@ class HostTable:
                                          C.c_float(delta_threshold), int(clear_dirty), C.byref(n)))
         return n.value
 
-    def load(self, directory: str, serving: bool = False) -> int:
+    def load(self, directory: str, serving: bool = False, rank: int = 0, world: int = 1) -> int:
+        """Load every ``part-*`` file of ``directory``.  With ``world`` > 1 only the keys that rank ``rank``
+        owns are kept, whatever number of ranks wrote the files (resharding on load)."""
         total = 0
         for name in sorted(os.listdir(directory)):
             if not name.startswith("part-"):
                 continue
             n = C.c_int64()
-            N.hcheck(N.host().pbh_table_load_file(self._h, os.path.join(directory, name).encode(), int(serving),
-                                                  C.byref(n)))
+            N.hcheck(N.host().pbh_table_load_file_owned(self._h, os.path.join(directory, name).encode(), int(serving),
+                                                        rank, world, C.byref(n)))
             total += n.value
         return total
 

@@ -407,3 +407,22 @@ def cpu_sharded_sparse_router(rank, world):
     assert np.mean(losses[-5:]) < np.mean(losses[:5]), losses
     box.end_pass()
     return (losses[0], losses[-1])
+
+
+def cpu_reshard_on_load(rank, world, ckpt):
+    """A model saved by one process loads into `world` ranks: every rank keeps exactly the keys it owns."""
+    from paddlebox_b200.box_wrapper import BoxWrapper, owner_of
+    box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=rank, world_size=world)
+    box.initialize_gpu_and_load_model({})
+    n = box.load_model(ckpt)
+    keys = box.host_table.keys()
+    assert n == keys.size and np.all(owner_of(keys, world) == rank)
+    rows = box.host_table.fetch_rows(keys, create=False)
+    assert np.allclose(rows[:, 2], (keys % 97).astype(np.float32))
+    tot = torch.tensor([n])
+    dist.all_reduce(tot)
+    # save again from `world` ranks into one directory: the union is the original model
+    out = ckpt + f"_resaved_{world}"
+    box.save_base(out)
+    dist.barrier()
+    return int(tot)

@@ -19,11 +19,11 @@ def _free_port():
     return p
 
 
-def _spawn(fn, world, backend, timeout=300):
+def _spawn(fn, world, backend, timeout=300, args=()):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=W.run, args=(fn, r, world, port, backend, q)) for r in range(world)]
+    procs = [ctx.Process(target=W.run, args=(fn, r, world, port, backend, q, *args)) for r in range(world)]
     for p in procs:
         p.start()
     results = {}
@@ -69,6 +69,23 @@ def test_multi_node_dense_sync_four_ranks_gloo():
 def test_sharded_sparse_over_all_to_all_gloo(world):
     outs = _spawn(W.cpu_sharded_sparse_router, world, "gloo")
     assert all(o[1] < o[0] for o in outs)
+
+
+def test_model_saved_by_one_rank_loads_into_three_and_back(tmp_path):
+    import numpy as np
+    from paddlebox_b200.host import HostTable
+    t = HostTable(4)
+    keys = np.arange(1, 2001, dtype=np.uint64)
+    rows = t.fetch_rows(keys)
+    rows[:, 2] = (keys % 97).astype(np.float32)
+    t.store_rows(keys, rows)
+    ckpt = str(tmp_path / "one")
+    assert t.save(ckpt) == 2000
+    outs = _spawn(W.cpu_reshard_on_load, 3, "gloo", args=(ckpt,))
+    assert outs == [2000, 2000, 2000]
+    t2 = HostTable(4)                                              # 3 ranks -> 1 process again
+    assert t2.load(ckpt + "_resaved_3") == 2000
+    assert np.allclose(t2.fetch_rows(keys, create=False), t.fetch_rows(keys, create=False), rtol=1e-6)
 
 
 def _ngpu():
