@@ -176,3 +176,47 @@ def test_serving_predictor_reproduces_training_predictions(tmp_path, box):
         assert np.array_equal(pred.box.host_table.fetch_rows(pred.box.host_table.keys(), create=False), rows_before)
     finally:
         pred.close()
+
+
+def test_next_pass_preloads_and_feeds_while_the_current_pass_trains(tmp_path, box):
+    """The PaddleBox pipeline: two datasets alternate; pass N+1 is read, parsed and fed (keys routed)
+    while pass N is still between begin_pass and end_pass."""
+    torch.manual_seed(0)
+    dss = []
+    for i in range(2):
+        d = tmp_path / f"p{i}"
+        d.mkdir()
+        ds = DatasetFactory().create_dataset("PadBoxSlotDataset")
+        ds.set_use_var(slot_vars(4, 2))
+        ds.set_batch_size(32)
+        ds.set_thread(2)
+        dss.append((ds, d))
+    model = CtrDnn(num_slots=4, embedx_dim=8, dense_dim=2, hidden=(16,))
+    trainer = CTRTrainer(model, box, TrainerConfig(dense_lr=1e-2))
+    box.init_metric("AucCalculator", "auc", "label", "pred", metric_phase=1, bucket_size=10000)
+
+    def files_for(p, d):
+        return write_files(str(d), n_files=1, lines_per_file=256, n_sparse=4, n_dense=2, key_space=60 + 20 * p, seed=p)
+
+    cur, cur_dir = dss[0]
+    cur.set_filelist(files_for(0, cur_dir))
+    cur.set_date("20240101")
+    cur.preload_into_memory()
+    cur.wait_preload_done()
+    seen = []
+    for p in range(4):
+        nxt, nxt_dir = dss[(p + 1) % 2]
+        cur.begin_pass()
+        in_hbm = set(box._pass_keys.tolist())
+        nxt.set_filelist(files_for(p + 1, nxt_dir))
+        nxt.preload_into_memory()                      # pass p+1 is read while pass p trains
+        stats = trainer.train_from_dataset(cur)
+        nxt.wait_preload_done()                        # ... and fed before pass p ends
+        assert set(box._pass_keys.tolist()) != in_hbm  # the NEXT pass's keys are already known
+        cur.end_pass(False)
+        assert stats["instances"] == 256
+        seen.append(box.get_metric_msg("auc")[0])
+        cur.release_memory()
+        cur = nxt
+    # every key of all four passes was created in the table and trained
+    assert box.host_table.size() > 4 * 60 and all(0.0 <= a <= 1.0 for a in seen)
