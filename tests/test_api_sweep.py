@@ -468,3 +468,22 @@ def test_numeric_gradient_checks_of_composed_ops():
     assert gradcheck(lambda x, ad: CO.fused_seq_tensor(x, ad, 2, 3, 3, 2, 1, 1)[0], (rnd(2, 2 * 3 * 3 * 2), rnd(2, 2 * 1 * 2)))
     assert gradcheck(lambda x: CO.filter_by_instag(x, [0, 1, 2, 3], torch.tensor([1, 2, 1]), [1])[0], (rnd(3, 4),))
     assert gradcheck(lambda a: CO.fused_concat([a, a * 2], 1, 2), (rnd(3, 4),))
+
+
+def test_layers_namespace_has_the_reference_names():
+    from paddlebox_b200 import layers
+    names = ("_pull_box_sparse _pull_box_extended_sparse _pull_gpups_sparse _store_q_value lookup_input "
+             "pull_cache_value data_norm continuous_value_model fused_seqpool_cvm fused_seqpool_cvm_with_diff_thres "
+             "fused_seqpool_cvm_with_conv fused_seqpool_cvm_with_pcoc fused_seqpool_cvm_tradew "
+             "fused_seqpool_cvm_with_credit cross_norm_layer_hadamard scaled_fc scaled_int8fc fused_seqpool_concat "
+             "fused_concat fused_seq_tensor rank_attention batch_fc shuffle_batch partial_concat partial_sum "
+             "tdm_child tdm_sampler filter_by_instag").split()
+    assert [n for n in names if not callable(getattr(layers, n, None))] == []
+    from paddlebox_b200.side_tables import GpuReplicaCache, InputTable
+    c = GpuReplicaCache(2)
+    c.add_items([1.0, 2.0]); c.add_items([3.0, 4.0])
+    c.to_hbm(torch.device("cpu"))
+    assert layers.pull_cache_value(c, torch.tensor([1, 0])).tolist() == [[3.0, 4.0], [1.0, 2.0]]
+    t = InputTable(1)
+    t.add_index_data("k", [9.0])
+    assert layers.lookup_input(t, torch.tensor([1, 0])).tolist() == [[9.0], [0.0]]
