@@ -220,3 +220,48 @@ def test_next_pass_preloads_and_feeds_while_the_current_pass_trains(tmp_path, bo
         cur = nxt
     # every key of all four passes was created in the table and trained
     assert box.host_table.size() > 4 * 60 and all(0.0 <= a <= 1.0 for a in seen)
+
+
+def test_join_and_update_phases_share_one_table(tmp_path, box):
+    """The two-program pattern of PaddleBox jobs: a join phase on PV-merged batches and an update phase on
+    plain instances, each with its own model and its own metric, flipping the phase between them."""
+    torch.manual_seed(0)
+    ds = DatasetFactory().create_dataset("PadBoxSlotDataset")
+    ds.set_use_var(slot_vars(4, 2))
+    ds.set_batch_size(32)
+    ds.set_thread(2)
+    ds.set_parse_logkey(True)
+    ds.set_enable_pv_merge(True)
+    ds.set_filelist(write_files(str(tmp_path), n_files=1, lines_per_file=192, n_sparse=4, n_dense=2, key_space=40,
+                                logkey=True))
+    ds.set_date("20240101")
+    box.init_metric("AucCalculator", "join_auc", "label", "pred", metric_phase=1, bucket_size=10000)
+    box.init_metric("AucCalculator", "update_auc", "label", "pred", metric_phase=0, bucket_size=10000)
+    join = CTRTrainer(CtrDnn(num_slots=4, embedx_dim=8, dense_dim=2, hidden=(16,)), box, TrainerConfig(dense_lr=1e-2))
+    update = CTRTrainer(CtrDnn(num_slots=4, embedx_dim=8, dense_dim=2, hidden=(8,)), box, TrainerConfig(dense_lr=1e-2))
+    ds.load_into_memory()
+    ds.begin_pass()
+    for rnd in range(2):
+        box.set_phase(1)                                   # join: page views stay together
+        ds.set_current_phase(1)
+        ds.preprocess_instance()
+        ds.prepare_train(1, 0)
+        sids = [b.meta["search_id"] for b in ds.batches(worker=0)]
+        for s in sids:                                      # instances of one page view are adjacent
+            uniq, counts = torch.unique_consecutive(s, return_counts=True)
+            assert uniq.numel() == torch.unique(s).numel()
+        st = join.train_from_dataset(ds)
+        assert st["instances"] == 192
+        ds.postprocess_instance()
+        box.flip_phase()                                    # update: plain shuffled instances
+        ds.set_current_phase(0)
+        ds.prepare_train(1, 0)
+        st = update.train_from_dataset(ds)
+        assert st["instances"] == 192 and box.phase() == 0
+        j, u = box.get_metric_msg("join_auc"), box.get_metric_msg("update_auc")
+        assert j[7] == 192 and u[7] == 192                  # each metric saw only its own phase
+    ds.end_pass(False)
+    # both phases pushed into the same table: every occurrence was shown twice per round, two rounds
+    rows = box.host_table.fetch_rows(box.host_table.keys(), create=False)
+    total_occurrences = ds._native.total_feasigns()
+    assert abs(rows[:, 0].sum() - 4 * total_occurrences) < 1e-3 * total_occurrences
