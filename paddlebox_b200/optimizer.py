@@ -110,3 +110,48 @@ class LocalSGD(GradAllReduce):
         if main_program is not None and getattr(main_program, "_pipeline_opt", None):
             main_program._pipeline_opt.sync_weight_step = self.k_steps
         return mode
+
+
+class SingleProcessMultiThread(GradAllReduce):
+    """``collective_mode = "single_process_multi_thread"``: one process driving all local GPUs with per-grad
+    allreduce (transpiler/collective.py:421-470).  Here every GPU has its own process; the sync mode is the
+    same per-step allreduce."""
+
+
+class DistributeTranspilerConfig:
+    """``fluid.DistributeTranspilerConfig``: ``mode`` must be ``"collective"``; ``collective_mode`` picks the
+    data-parallel scheme (``grad_allreduce``, ``local_sgd``, ``single_process_multi_thread``)."""
+
+    def __init__(self):
+        self.mode = "collective"
+        self.collective_mode = "grad_allreduce"
+        self.nccl_comm_num = 1
+        self.local_sgd_steps = 1
+
+
+class DistributeTranspiler:
+    """``fluid.DistributeTranspiler(config).transpile(trainer_id, program=..., trainers=..., ...)`` as the
+    reference's BoxPS test drives it (test_boxps.py:27-72): picks the collective scheme and stamps it on the
+    program's trainer configuration."""
+
+    _MODES = {"grad_allreduce": GradAllReduce, "local_sgd": LocalSGD,
+              "single_process_multi_thread": SingleProcessMultiThread}
+
+    def __init__(self, config: DistributeTranspilerConfig | None = None):
+        self.config = config or DistributeTranspilerConfig()
+        self.impl = None
+
+    def transpile(self, trainer_id: int = 0, program=None, pservers: str = "", trainers="127.0.0.1:6174",
+                  sync_mode: bool = True, startup_program=None, current_endpoint: str = "127.0.0.1:6174"):
+        if self.config.mode != "collective":
+            raise ValueError("only config.mode = 'collective' exists here: the parameter server lives in the GPUs")
+        cls = self._MODES.get(self.config.collective_mode)
+        if cls is None:
+            raise ValueError(f"invalid collective_mode {self.config.collective_mode!r}")
+        endpoints = trainers.split(",") if isinstance(trainers, str) else list(trainers)
+        if cls is GradAllReduce and len(endpoints) == 1 and self.config.collective_mode == "grad_allreduce":
+            # the reference refuses a multi-process scheme with a single endpoint (collective.py:82-88)
+            raise ValueError("grad_allreduce needs more than one trainer endpoint")
+        self.impl = cls(k_steps=self.config.local_sgd_steps) if cls is LocalSGD else cls(self.config.nccl_comm_num)
+        return self.impl.transpile(startup_program, program, rank=trainer_id, endpoints=endpoints,
+                                   current_endpoint=current_endpoint)

@@ -487,3 +487,26 @@ def test_layers_namespace_has_the_reference_names():
     t = InputTable(1)
     t.add_index_data("k", [9.0])
     assert layers.lookup_input(t, torch.tensor([1, 0])).tolist() == [[9.0], [0.0]]
+
+
+def test_distribute_transpiler_shim_follows_test_boxps():
+    import torch.nn as nn
+    from paddlebox_b200.optimizer import (Adam, BoxPSOptimizer, DistributeTranspiler, DistributeTranspilerConfig,
+                                          GradAllReduce, LocalSGD)
+    prog = nn.Linear(2, 1)
+    BoxPSOptimizer(Adam(1e-3)).minimize(prog)
+    cfg = DistributeTranspilerConfig()
+    cfg.collective_mode = "single_process_multi_thread"
+    assert DistributeTranspiler(cfg).transpile(trainer_id=0, program=prog, trainers="127.0.0.1:6174") == "allreduce"
+    cfg.collective_mode = "grad_allreduce"
+    with pytest.raises(ValueError):
+        DistributeTranspiler(cfg).transpile(trainer_id=0, program=prog, trainers="127.0.0.1:6174")
+    assert DistributeTranspiler(cfg).transpile(0, program=prog, trainers="a:1,b:2") == "allreduce"
+    cfg.collective_mode, cfg.local_sgd_steps = "local_sgd", 4
+    assert DistributeTranspiler(cfg).transpile(0, program=prog, trainers="a:1,b:2") == "kstep"
+    assert prog._pipeline_opt.sync_dense_mode == "kstep" and prog._pipeline_opt.sync_weight_step == 4
+    cfg.collective_mode = "nope"
+    with pytest.raises(ValueError):
+        DistributeTranspiler(cfg).transpile(0, program=prog)
+    assert GradAllReduce(0).transpile(main_program=prog, rank=1, endpoints="x", current_endpoint="x") == "allreduce"
+    assert LocalSGD(0).transpile(main_program=prog) == "kstep"
