@@ -193,6 +193,10 @@ def main():
     from paddlebox_b200.models.ctr import CtrDnn, DeepFM, MMoE, WideDeep
     from paddlebox_b200.ops.pull_box_sparse import SlotBatch
     from paddlebox_b200.trainer import CTRTrainer, TrainerConfig
+    from paddlebox_b200.flags import FLAGS
+    # every number in profiles/ was measured with the trainer thread left to the scheduler: keep that setup
+    # (thread pinning, FLAGS_enable_binding_train_cpu, has not been measured on a GPU box yet)
+    FLAGS.enable_binding_train_cpu = False
     lib = N.cuda()
     lib.pbx_launch_count.restype = C.c_longlong
 

@@ -169,6 +169,10 @@ int pbh_dataset_set_str(void* h, const char* key, const char* v) {
 }
 int pbh_dataset_save_arena(void* h, const char* path) { return ((Dataset*)h)->save_arena(path); }
 int pbh_dataset_load_arena(void* h, const char* path) { return ((Dataset*)h)->load_arena(path); }
+int pbh_dataset_set_reader_cores(void* h, const int* cores, int n) {
+  ((Dataset*)h)->reader_cores.assign(cores, cores + n);
+  return 0;
+}
 int pbh_dataset_set_omit_slots(void* h, const int* slot_indices, int n) {
   ((Dataset*)h)->omit_slots.assign(slot_indices, slot_indices + n);
   return 0;

@@ -593,6 +593,11 @@ int Dataset::load_into_memory() {
   int nr = std::max(1, thread_num), nm = std::max(1, merge_thread_num);
   for (int i = 0; i < nm; ++i) mergers.emplace_back([this] { merge_loop(); });
   for (int i = 0; i < nr; ++i) readers.emplace_back([&] { reader_loop(&next_file, &errors); });
+  if (!reader_cores.empty()) {
+    size_t c = 0;
+    for (auto& th : readers) ThreadPool::set_cpu_affinity(th, reader_cores[c++ % reader_cores.size()]);
+    for (auto& th : mergers) ThreadPool::set_cpu_affinity(th, reader_cores[c++ % reader_cores.size()]);
+  }
   for (auto& th : readers) th.join();
   chan_.close();
   for (auto& th : mergers) th.join();

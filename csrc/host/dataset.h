@@ -204,6 +204,9 @@ class Dataset {
   // string key -> row offset index of the InputTable (pbh_input_index_*); when set, a parser plugin
   // that exports pbx_set_offset_func receives the lookup callback (GetOffsetFunc, data_feed.cc:4487)
   void* input_index = nullptr;
+  // cores the reader / merge threads are pinned to, round-robin (boxps::get_readins_cores,
+  // data_set.cc:2028; FLAGS_enable_binding_train_cpu); empty = not pinned
+  std::vector<int> reader_cores;
   // slots (indices into `slots`) whose feasigns are NOT parameter-server keys: left out of the feed
   // pass (slot_omit_in_feedpass, data_feed.cc:3119-3146)
   std::vector<int> omit_slots;

@@ -119,6 +119,8 @@ uint64_t pbh_input_index_miss(void* ix);
 int pbh_dataset_save_arena(void* ds, const char* path);
 int pbh_dataset_load_arena(void* ds, const char* path);
 int pbh_dataset_set_input_index(void* ds, void* ix);
+/* reader / merge threads are pinned round-robin to these cores (get_readins_cores, data_set.cc:2028) */
+int pbh_dataset_set_reader_cores(void* ds, const int* cores, int n);
 /* slots (indices in set_slots order) whose feasigns are not PS keys: skipped by the key collection
  * (slot_omit_in_feedpass of InitializeGPUAndLoadModel, data_feed.cc:3119-3146) */
 int pbh_dataset_set_omit_slots(void* ds, const int* slot_indices, int n);

@@ -316,6 +316,10 @@ class NativeDataset:
         else:
             N.hcheck(lib.pbh_dataset_set_int(self._h, key.encode(), C.c_int64(int(value))))
 
+    def set_reader_cores(self, cores: Sequence[int]):
+        arr = (C.c_int * len(cores))(*cores)
+        N.hcheck(N.host().pbh_dataset_set_reader_cores(self._h, arr, len(cores)))
+
     def set_omit_slots(self, slot_indices: Sequence[int]):
         arr = (C.c_int * len(slot_indices))(*slot_indices)
         N.hcheck(N.host().pbh_dataset_set_omit_slots(self._h, arr, len(slot_indices)))

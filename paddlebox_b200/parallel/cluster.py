@@ -134,17 +134,20 @@ def exec_range_func(n: int, fn: Callable[[int, int], None], parts: int | None = 
         f.result()
 
 
+# cores of this process as they were when the module was imported: pinning one thread later must not
+# shrink what the other helpers see
+_PROCESS_CORES = sorted(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else list(range(os.cpu_count() or 1))
+
+
 def get_train_cores() -> list:
     """Cores the trainer threads may be pinned to (boxps::get_train_cores, boxps_trainer.cc:179):
-    the first half of this process's affinity mask."""
-    cores = sorted(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else list(range(os.cpu_count() or 1))
-    return cores[:max(1, len(cores) // 2)]
+    the first half of this process's cores."""
+    return _PROCESS_CORES[:max(1, len(_PROCESS_CORES) // 2)]
 
 
 def get_readins_cores() -> list:
     """Cores for the reader threads (boxps::get_readins_cores, data_set.cc:2028): the other half."""
-    cores = sorted(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else list(range(os.cpu_count() or 1))
-    return cores[len(cores) // 2:] or cores
+    return _PROCESS_CORES[len(_PROCESS_CORES) // 2:] or _PROCESS_CORES
 
 
 def set_cpu_affinity(cores: Sequence[int]) -> bool:

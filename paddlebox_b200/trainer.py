@@ -72,6 +72,7 @@ class CTRTrainer:
         if self.world > 1:
             self.store.broadcast_params(0)
             self.store.mark_dirty()
+        self.pinned_cores = self._bind_train_cpu()
         self.timers = CudaStageTimers(self.cfg.debug)
         self.dumper = None
         if self.cfg.dump_fields_path and (self.cfg.dump_fields or self.cfg.dump_param):
@@ -83,6 +84,20 @@ class CTRTrainer:
         for m in model.modules():
             if getattr(m, "sync_stats", False) and self.world > 1:
                 m.reduce_fn = self._reduce_stats
+
+    def _bind_train_cpu(self) -> list:
+        """FLAGS_enable_binding_train_cpu (boxps_trainer.cc:165-193): the training thread of this process is
+        pinned to its share of the train cores — the processes of one node split them by local rank.  Only
+        with several processes per node; a lone process keeps the scheduler's choice."""
+        import os
+        from .parallel.cluster import get_train_cores, set_cpu_affinity
+        local_world = int(os.environ.get("LOCAL_WORLD_SIZE", "1"))
+        if not FLAGS.enable_binding_train_cpu or local_world <= 1:
+            return []
+        cores = get_train_cores()
+        local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+        mine = cores[local_rank::local_world] or cores
+        return list(mine) if set_cpu_affinity(mine) else []
 
     def _reduce_stats(self, stats: torch.Tensor) -> torch.Tensor:
         import torch.distributed as dist

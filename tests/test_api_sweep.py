@@ -510,3 +510,32 @@ def test_distribute_transpiler_shim_follows_test_boxps():
         DistributeTranspiler(cfg).transpile(0, program=prog)
     assert GradAllReduce(0).transpile(main_program=prog, rank=1, endpoints="x", current_endpoint="x") == "allreduce"
     assert LocalSGD(0).transpile(main_program=prog) == "kstep"
+
+
+def test_cpu_binding_of_reader_and_trainer_threads(tmp_path, box, monkeypatch):
+    """FLAGS_enable_binding_train_cpu: reader threads on the read-ins cores, the trainer on its share."""
+    import threading
+    from paddlebox_b200.flags import FLAGS
+    from paddlebox_b200.models.ctr import CtrDnn
+    from paddlebox_b200.parallel.cluster import get_readins_cores, get_train_cores
+    from paddlebox_b200.trainer import CTRTrainer
+    assert FLAGS.enable_binding_train_cpu
+    ds = DatasetFactory().create_dataset("InMemoryDataset")
+    ds.set_use_var(slot_vars(2, 1))
+    ds.set_thread(3)
+    ds.set_filelist(write_files(str(tmp_path), n_files=3, lines_per_file=50, n_sparse=2, n_dense=1, key_space=20))
+    ds.load_into_memory()                                    # pinned readers still read everything
+    assert ds.get_memory_data_size() == 150
+    if len(os.sched_getaffinity(0)) < 4:
+        pytest.skip("needs >= 4 cores to split")
+    before = os.sched_getaffinity(threading.get_native_id())
+    try:
+        assert CTRTrainer(CtrDnn(num_slots=2, embedx_dim=4, dense_dim=1, hidden=(4,)), box).pinned_cores == []
+        monkeypatch.setenv("LOCAL_WORLD_SIZE", "2")
+        monkeypatch.setenv("LOCAL_RANK", "1")
+        tr = CTRTrainer(CtrDnn(num_slots=2, embedx_dim=4, dense_dim=1, hidden=(4,)), box)
+        train = get_train_cores()
+        assert tr.pinned_cores == train[1::2] and os.sched_getaffinity(threading.get_native_id()) == set(train[1::2])
+        assert not set(tr.pinned_cores) & set(get_readins_cores()) or len(before) < 2
+    finally:
+        os.sched_setaffinity(threading.get_native_id(), before)
