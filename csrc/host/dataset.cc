@@ -591,13 +591,19 @@ int Dataset::load_into_memory() {
   std::atomic<int> errors{0};
   std::vector<std::thread> readers, mergers;
   int nr = std::max(1, thread_num), nm = std::max(1, merge_thread_num);
-  for (int i = 0; i < nm; ++i) mergers.emplace_back([this] { merge_loop(); });
-  for (int i = 0; i < nr; ++i) readers.emplace_back([&] { reader_loop(&next_file, &errors); });
-  if (!reader_cores.empty()) {
-    size_t c = 0;
-    for (auto& th : readers) ThreadPool::set_cpu_affinity(th, reader_cores[c++ % reader_cores.size()]);
-    for (auto& th : mergers) ThreadPool::set_cpu_affinity(th, reader_cores[c++ % reader_cores.size()]);
-  }
+  // every thread pins ITSELF: pinning from here through the std::thread handle would race with short-lived
+  // threads — a thread that has already exited has tid 0 in glibc, and sched_setaffinity(0, ...) then pins
+  // the caller instead
+  auto pin_self = [this](size_t k) {
+    if (reader_cores.empty()) return;
+    cpu_set_t set;
+    CPU_ZERO(&set);
+    CPU_SET(reader_cores[k % reader_cores.size()], &set);
+    pthread_setaffinity_np(pthread_self(), sizeof(set), &set);
+  };
+  for (int i = 0; i < nm; ++i) mergers.emplace_back([this, pin_self, i, nr] { pin_self((size_t)(nr + i)); merge_loop(); });
+  for (int i = 0; i < nr; ++i)
+    readers.emplace_back([&, pin_self, i] { pin_self((size_t)i); reader_loop(&next_file, &errors); });
   for (auto& th : readers) th.join();
   chan_.close();
   for (auto& th : mergers) th.join();

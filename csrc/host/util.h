@@ -129,6 +129,8 @@ class ThreadPool {
     }
     for (auto& f : fs) f.get();
   }
+  // (only for threads known to be alive: an exited, unjoined thread has tid 0 and the call would pin the
+  //  CALLER — short-lived threads must pin themselves with pthread_self())
   static bool set_cpu_affinity(std::thread& t, int core);
 
  private:
