@@ -360,16 +360,18 @@ class InMemoryDataset(DatasetBase):
         self._native.set("world", world)
 
     # pass data ---------------------------------------------------------------------------------
-    def _bind_reader_cores(self):
-        """FLAGS_enable_binding_train_cpu: reader / merge threads go to the read-ins half of this process's
-        cores (data_set.cc:2028), leaving the other half to the training threads."""
-        if FLAGS.enable_binding_train_cpu:
+    def _bind_reader_cores(self, overlapped: bool):
+        """FLAGS_enable_binding_train_cpu: while a pass is PRE-loaded next to a training pass, reader / merge
+        threads go to the read-ins half of this process's cores (data_set.cc:2028) and leave the other half to
+        the training threads.  A synchronous load has the machine to itself and stays unpinned."""
+        cores = []
+        if overlapped and FLAGS.enable_binding_train_cpu:
             from .parallel.cluster import get_readins_cores
             cores = get_readins_cores()
-            self._native.set_reader_cores(cores if len(cores) > 1 else [])
+        self._native.set_reader_cores(cores if len(cores) > 1 else [])
 
     def load_into_memory(self):
-        self._bind_reader_cores()
+        self._bind_reader_cores(False)
         self._native.load_into_memory()
         if self._merge_by_lineid:
             self.merge_by_ins_id()
@@ -379,7 +381,7 @@ class InMemoryDataset(DatasetBase):
         thread_num = thread_num or getattr(self, "preload_thread_num", None)
         if thread_num:
             self.set_thread(thread_num)
-        self._bind_reader_cores()
+        self._bind_reader_cores(True)
         self._native.preload_into_memory()
 
     def wait_preload_done(self):
