@@ -1,0 +1,177 @@
+// Sanitizer driver for the host runtime: links csrc/host/*.cc directly and drives the C ABI the way the
+// Python layer does — multi-threaded text load with key collection, batch dealing, concurrent packing from
+// several threads, archive and pass-file round trips, host table bulk ops, SSD spill / promote, key sort.
+// Built three times by benchmarks/sanitize_host.sh: -fsanitize=address,undefined, -fsanitize=thread, plain.
+#include <atomic>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "../../../include/pbx_host.h"
+
+#define OK(call)                                                                          \
+  do {                                                                                    \
+    if ((call) != 0) {                                                                    \
+      fprintf(stderr, "FAILED %s:%d %s: %s\n", __FILE__, __LINE__, #call, pbh_last_error()); \
+      return 1;                                                                           \
+    }                                                                                     \
+  } while (0)
+#define CHECK(c)                                                       \
+  do {                                                                 \
+    if (!(c)) { fprintf(stderr, "FAILED %s:%d %s\n", __FILE__, __LINE__, #c); return 1; } \
+  } while (0)
+
+static void* make_dataset(int S) {
+  void* ds = nullptr;
+  pbh_dataset_create(&ds);
+  std::vector<std::string> names = {"label", "dense"};
+  std::vector<int> types = {1, 1}, dense = {1, 1}, used = {1, 1}, dims = {1, 3};
+  for (int s = 0; s < S; ++s) { names.push_back("s" + std::to_string(s)); types.push_back(0); dense.push_back(0); used.push_back(1); dims.push_back(1); }
+  std::vector<const char*> np;
+  for (auto& n : names) np.push_back(n.c_str());
+  pbh_dataset_set_slots(ds, (int)np.size(), np.data(), types.data(), dense.data(), used.data(), dims.data());
+  return ds;
+}
+
+int main(int argc, char** argv) {
+  const std::string dir = argc > 1 ? argv[1] : "/tmp";
+  const int S = 6, FILES = 4, LINES = 3000;
+  std::vector<std::string> files;
+  unsigned rng = 12345;
+  auto rnd = [&] { rng = rng * 1103515245u + 12345u; return (rng >> 8) & 0xffffff; };
+  for (int f = 0; f < FILES; ++f) {
+    files.push_back(dir + "/san-" + std::to_string(f) + ".txt");
+    FILE* fp = fopen(files.back().c_str(), "w");
+    CHECK(fp != nullptr);
+    for (int i = 0; i < LINES; ++i) {
+      fprintf(fp, "1 %d 3 0.5 0.25 %g", (int)(rnd() & 1), (rnd() % 100) / 100.0 + 0.01);
+      for (int s = 0; s < S; ++s) {
+        int n = 1 + rnd() % 3;
+        fprintf(fp, " %d", n);
+        for (int k = 0; k < n; ++k) fprintf(fp, " %u", 1 + rnd() % 5000 + s * 5000);
+      }
+      fputc('\n', fp);
+    }
+    fclose(fp);
+  }
+  std::vector<const char*> fptr;
+  for (auto& f : files) fptr.push_back(f.c_str());
+
+  void* ds = make_dataset(S);
+  OK(pbh_dataset_set_filelist(ds, FILES, fptr.data()));
+  OK(pbh_dataset_set_int(ds, "thread_num", 4));
+  OK(pbh_dataset_set_int(ds, "merge_thread_num", 3));
+  OK(pbh_dataset_set_int(ds, "batch_size", 128));
+  OK(pbh_dataset_preload_into_memory(ds));
+  OK(pbh_dataset_wait_preload_done(ds));
+  CHECK(pbh_dataset_num_records(ds) == FILES * LINES);
+  int64_t nuniq = pbh_dataset_unique_keys(ds, nullptr, 0);
+  CHECK(nuniq > 1000);
+  OK(pbh_dataset_prepare_train(ds, 3, 1, 7, 0));
+  // concurrent packing: 3 workers x 2 threads each, interleaved batches
+  std::atomic<int> bad{0};
+  std::atomic<long long> key_sum{0};
+  std::vector<std::thread> packers;
+  for (int w = 0; w < 3; ++w)
+    for (int t = 0; t < 2; ++t)
+      packers.emplace_back([&, w, t] {
+        int64_t nb = pbh_dataset_num_batches(ds, w);
+        for (int64_t b = t; b < nb; b += 2) {
+          int B = 0; int64_t nk = 0;
+          if (pbh_dataset_batch_shape(ds, w, b, &B, &nk) != 0) { ++bad; return; }
+          std::vector<uint64_t> keys((size_t)nk + 1);
+          std::vector<int32_t> off((size_t)B * (S + 1) + S * B + 2);
+          std::vector<float> dense((size_t)B * 4);
+          if (pbh_dataset_pack_batch(ds, w, b, keys.data(), off.data(), dense.data(), (int)(b & 1)) != 0) { ++bad; return; }
+          long long s = 0;
+          for (int64_t i = 0; i < nk; ++i) s += (long long)keys[i];
+          key_sum += s;
+        }
+      });
+  for (auto& th : packers) th.join();
+  CHECK(bad.load() == 0 && key_sum.load() > 0);
+  // archive + pass file round trips
+  const std::string arc = dir + "/san.archive", arena = dir + "/san.arena";
+  OK(pbh_dataset_save_archive(ds, arc.c_str()));
+  OK(pbh_dataset_save_arena(ds, arena.c_str()));
+  void* ds2 = make_dataset(S);
+  OK(pbh_dataset_set_int(ds2, "batch_size", 128));
+  OK(pbh_dataset_load_archive(ds2, arc.c_str()));
+  CHECK(pbh_dataset_num_records(ds2) == FILES * LINES);
+  OK(pbh_dataset_load_arena(ds2, arena.c_str()));
+  CHECK(pbh_dataset_num_records(ds2) == FILES * LINES && pbh_dataset_unique_keys(ds2, nullptr, 0) == nuniq);
+  OK(pbh_dataset_prepare_train(ds2, 2, 1, 3, 0));
+  {
+    int B = 0; int64_t nk = 0;
+    OK(pbh_dataset_batch_shape(ds2, 1, 0, &B, &nk));
+    std::vector<uint64_t> keys((size_t)nk + 1);
+    std::vector<int32_t> off((size_t)B * (S + 1) + S * B + 2);
+    std::vector<float> dense((size_t)B * 4);
+    OK(pbh_dataset_pack_batch(ds2, 1, 0, keys.data(), off.data(), dense.data(), 0));
+    OK(pbh_dataset_pack_batch(ds2, 1, 0, keys.data(), off.data(), dense.data(), 1));
+  }
+  CHECK(pbh_dataset_slots_shuffle(ds2, nullptr, 0, 1) != 0);          // refused on a pass file
+  OK(pbh_dataset_release_memory(ds2));
+  OK(pbh_dataset_destroy(ds2));
+  std::vector<uint64_t> uk((size_t)nuniq);
+  pbh_dataset_unique_keys(ds, uk.data(), nuniq);
+  OK(pbh_dataset_destroy(ds));
+
+  // host table: bulk create / pull / push from the pool, SSD tier, resharded load
+  PbxSparseOptConfig cfg;
+  memset(&cfg, 0, sizeof(cfg));
+  cfg.nonclk_coeff = 0.1f; cfg.clk_coeff = 1.f; cfg.min_bound = -10; cfg.max_bound = 10; cfg.learning_rate = 0.05f;
+  cfg.initial_g2sum = 3; cfg.mf_create_thresholds = 0; cfg.mf_learning_rate = 0.05f; cfg.mf_initial_g2sum = 3;
+  cfg.mf_initial_range = 1e-3f; cfg.mf_min_bound = -10; cfg.mf_max_bound = 10;
+  void* tab = nullptr;
+  OK(pbh_table_create(&tab, 8, 0, &cfg, 1));
+  PbxRowLayout L = pbx_make_layout(8, 0);
+  std::vector<float> rows(uk.size() * (size_t)L.stride);
+  OK(pbh_table_fetch_rows(tab, uk.data(), (int64_t)uk.size(), rows.data(), 1));
+  std::vector<float> push(uk.size() * (size_t)L.push_stride, 0.f);
+  for (size_t i = 0; i < uk.size(); ++i) { push[i * L.push_stride + 1] = 1.f; push[i * L.push_stride + 3] = 0.1f; }
+  OK(pbh_table_push(tab, uk.data(), (int64_t)uk.size(), push.data(), L.push_stride));
+  std::vector<float> pulled(uk.size() * 11);
+  OK(pbh_table_pull(tab, uk.data(), (int64_t)uk.size(), pulled.data(), 11));
+  const std::string ck = dir + "/san-ckpt", ssd = dir + "/san-ssd";
+  std::string mk = "mkdir -p " + ck + " " + ssd;
+  CHECK(system(mk.c_str()) == 0);
+  int64_t nsaved = 0;
+  OK(pbh_table_save(tab, ck.c_str(), 1, 0, 0.f, 0.f, 1, &nsaved));        // delta: clears the dirty flags
+  OK(pbh_table_ssd_open(tab, ssd.c_str()));
+  CHECK(pbh_table_spill(tab, -1.f, (int64_t)uk.size() / 3) > 0);
+  OK(pbh_table_pull(tab, uk.data(), (int64_t)uk.size() / 2, pulled.data(), 11));   // promotes half
+  OK(pbh_table_save(tab, ck.c_str(), 0, 0, 0.f, 0.f, 0, &nsaved));
+  CHECK(nsaved == (int64_t)uk.size());
+  CHECK(pbh_table_load_ssd2mem(tab) >= 0 && pbh_table_ssd_rows(tab) == 0);
+  void* tab2 = nullptr;
+  OK(pbh_table_create(&tab2, 8, 0, &cfg, 2));
+  int64_t n0 = 0, total = 0;
+  for (int shard = 0; shard < 64; ++shard) {
+    char name[600];
+    snprintf(name, sizeof(name), "%s/part-000-%05d", ck.c_str(), shard);
+    OK(pbh_table_load_file_owned(tab2, name, 0, 1, 3, &n0));
+    total += n0;
+  }
+  CHECK(total > 0 && total < (int64_t)uk.size() && pbh_table_size(tab2) == total);
+  OK(pbh_table_ssd_close(tab, 1));
+  OK(pbh_table_destroy(tab));
+  OK(pbh_table_destroy(tab2));
+
+  // key sort / partition
+  std::vector<uint64_t> raw(400000);
+  for (auto& k : raw) k = ((uint64_t)rnd() << 20) ^ rnd();
+  std::vector<uint64_t> copy = raw;
+  int64_t nu = pbh_sort_unique_u64(copy.data(), (int64_t)copy.size());
+  CHECK(nu > 0 && nu <= (int64_t)raw.size());
+  for (int64_t i = 1; i < nu; ++i) CHECK(copy[i - 1] < copy[i]);
+  std::vector<uint64_t> parted((size_t)nu);
+  int64_t counts[5];
+  OK(pbh_partition_by_owner(copy.data(), nu, 5, parted.data(), counts));
+  CHECK(counts[0] + counts[1] + counts[2] + counts[3] + counts[4] == nu);
+  printf("sanitize driver ok: %lld records, %lld unique keys\n", (long long)FILES * LINES, (long long)nuniq);
+  return 0;
+}
