@@ -172,6 +172,86 @@ int main(int argc, char** argv) {
   int64_t counts[5];
   OK(pbh_partition_by_owner(copy.data(), nu, 5, parted.data(), counts));
   CHECK(counts[0] + counts[1] + counts[2] + counts[3] + counts[4] == nu);
+  // graph store: build, threaded sampling and walks
+  {
+    void* g = nullptr;
+    OK(pbh_graph_create(&g));
+    std::vector<uint64_t> src, dst;
+    for (int i = 0; i < 20000; ++i) { src.push_back(1 + rnd() % 3000); dst.push_back(1 + rnd() % 3000); }
+    OK(pbh_graph_add_edges(g, 0, src.data(), dst.data(), (int64_t)src.size(), 0));
+    OK(pbh_graph_add_edges(g, 1, src.data(), dst.data(), (int64_t)src.size(), 1));
+    OK(pbh_graph_build(g, 0));
+    OK(pbh_graph_build(g, 1));
+    int64_t nn = pbh_graph_num_nodes(g, 0);
+    std::vector<uint64_t> ids((size_t)nn), nb((size_t)nn * 4), walks((size_t)nn * 6);
+    std::vector<int64_t> rp((size_t)nn + 1), col((size_t)pbh_graph_num_edges(g, 0));
+    std::vector<int32_t> cnt((size_t)nn), len((size_t)nn);
+    OK(pbh_graph_export_csr(g, 0, ids.data(), rp.data(), col.data()));
+    OK(pbh_graph_sample_neighbors(g, 0, ids.data(), nn, 4, 9, nb.data(), cnt.data()));
+    int meta[2] = {0, 1};
+    OK(pbh_graph_random_walk(g, meta, 2, ids.data(), nn, 6, 3, walks.data(), len.data()));
+    for (int64_t i = 0; i < nn; ++i) CHECK(len[i] >= 1 && len[i] <= 6 && cnt[i] >= 0 && cnt[i] <= 4);
+    OK(pbh_graph_destroy(g));
+  }
+  // metrics: concurrent adds, WuAUC, state export / import
+  {
+    void* a = nullptr;
+    OK(pbh_auc_create(&a, 10000));
+    std::vector<std::thread> ths;
+    for (int t = 0; t < 4; ++t)
+      ths.emplace_back([&, t] {
+        std::vector<float> p(5000), y(5000);
+        std::vector<uint64_t> uid(5000);
+        unsigned r = 77u + (unsigned)t;
+        for (size_t i = 0; i < p.size(); ++i) { r = r * 1664525u + 1013904223u; p[i] = (r >> 8) / 16777216.f; y[i] = (r & 64) ? 1.f : 0.f; uid[i] = r % 50; }
+        pbh_auc_add(a, p.data(), y.data(), nullptr, (int64_t)p.size(), 0);
+        pbh_auc_add_uid(a, p.data(), y.data(), uid.data(), (int64_t)p.size());
+      });
+    for (auto& th : ths) th.join();
+    double out8[8], out4[4];
+    std::vector<double> tab(2 * 10000), sums(5);
+    OK(pbh_auc_compute(a, out8));
+    OK(pbh_auc_compute_wuauc(a, out4));
+    CHECK(out8[7] == 20000 && out8[0] > 0.3 && out8[0] < 0.7);
+    OK(pbh_auc_export(a, tab.data(), sums.data()));
+    OK(pbh_auc_import(a, tab.data(), sums.data()));
+    OK(pbh_auc_destroy(a));
+  }
+  // async dense table: pushes from two threads while a third pulls
+  {
+    void* ad = nullptr;
+    OK(pbh_async_dense_create(&ad, 4096, 0.01f, 3, 4));
+    std::vector<float> w(4096, 0.5f);
+    OK(pbh_async_dense_set_params(ad, w.data()));
+    OK(pbh_async_dense_set_lr_range(ad, 0, 100, 0.f));
+    std::vector<std::thread> ths;
+    for (int t = 0; t < 2; ++t)
+      ths.emplace_back([&] { std::vector<float> g(4096, 0.1f); for (int i = 0; i < 20; ++i) pbh_async_dense_push(ad, g.data()); });
+    ths.emplace_back([&] { std::vector<float> o(4096); for (int i = 0; i < 20; ++i) pbh_async_dense_pull(ad, o.data()); });
+    for (auto& th : ths) th.join();
+    OK(pbh_async_dense_wait(ad));
+    OK(pbh_async_dense_pull(ad, w.data()));
+    CHECK(w[0] == 0.5f && w[200] < 0.5f && pbh_async_dense_updates(ad) > 0);
+    OK(pbh_async_dense_destroy(ad));
+  }
+  // input index from several threads
+  {
+    void* ix = nullptr;
+    OK(pbh_input_index_create(&ix));
+    std::vector<std::thread> ths;
+    for (int t = 0; t < 4; ++t)
+      ths.emplace_back([&, t] {
+        for (int i = 0; i < 2000; ++i) {
+          std::string k = "key" + std::to_string((i * 7 + t) % 500);
+          int fresh = 0;
+          pbh_input_index_add(ix, k.c_str(), k.size(), &fresh);
+          pbh_input_index_get(ix, k.c_str(), k.size());
+        }
+      });
+    for (auto& th : ths) th.join();
+    CHECK(pbh_input_index_size(ix) == 500 && pbh_input_index_miss(ix) == 0);
+    OK(pbh_input_index_destroy(ix));
+  }
   printf("sanitize driver ok: %lld records, %lld unique keys\n", (long long)FILES * LINES, (long long)nuniq);
   return 0;
 }

@@ -102,6 +102,26 @@ int64_t pbh_sort_unique_u64(uint64_t* keys, int64_t n);
 /* keys grouped by owning rank (owner = pbx_owner_of): out = rank 0's keys, rank 1's, ...; counts[r] */
 int pbh_partition_by_owner(const uint64_t* keys, int64_t n, int nranks, uint64_t* out, int64_t* counts);
 
+/* ---- graph store (csrc/host/graph.cc) ---------------------------------------------------
+ * reference: GraphGpuWrapper / GpuPsGraphTable (heter_ps/graph_gpu_wrapper.h:34-99,
+ * graph_gpu_ps_table_inl.cu), GraphDataGenerator walks (data_feed.cu:200-1206).  Edge type = small int;
+ * node ids are arbitrary uint64, mapped to dense indices in sorted-id order inside a type. */
+int pbh_graph_create(void** out);
+int pbh_graph_destroy(void* g);
+int pbh_graph_add_edges(void* g, int type, const uint64_t* src, const uint64_t* dst, int64_t n, int reverse);
+int pbh_graph_load_edge_file(void* g, int type, const char* path, int reverse, int64_t* n_loaded);
+int pbh_graph_build(void* g, int type);                     /* edge list -> CSR */
+int64_t pbh_graph_num_nodes(void* g, int type);
+int64_t pbh_graph_num_edges(void* g, int type);
+int pbh_graph_num_types(void* g);
+int pbh_graph_export_csr(void* g, int type, uint64_t* node_ids, int64_t* row_ptr, int64_t* col);
+/* up to k neighbours per node without replacement into out[i*k..], counts into out_cnt[i] */
+int pbh_graph_sample_neighbors(void* g, int type, const uint64_t* nodes, int64_t n, int k, uint64_t seed,
+                               uint64_t* out, int32_t* out_cnt);
+/* walks [n, walk_len]; step s follows edge type metapath[s % n_meta]; out_len = valid prefix length */
+int pbh_graph_random_walk(void* g, const int* metapath, int n_meta, const uint64_t* starts, int64_t n,
+                          int walk_len, uint64_t seed, uint64_t* out, int32_t* out_len);
+
 /* InputTable key index: string key -> row offset, 0 = miss (InputTable::AddIndexData / GetIndexOffset,
  * fleet/box_wrapper.h:124-197).  Attached to a dataset, a parser plugin that also exports
  *   void pbx_set_offset_func(uint64_t (*fn)(void* user, const char* key, size_t len), void* user)
