@@ -539,3 +539,16 @@ def test_cpu_binding_of_reader_and_trainer_threads(tmp_path, box, monkeypatch):
         assert not set(tr.pinned_cores) & set(get_readins_cores()) or len(before) < 2
     finally:
         os.sched_setaffinity(threading.get_native_id(), before)
+
+
+def test_capacity_planner_for_the_headline_config():
+    from paddlebox_b200.utils.capacity import plan
+    # BASELINE config 3: 125 M keys / GPU, dim 16, adagrad, ~320 K keys per batch, 8 GPUs
+    b = plan(125_000_000, 16, "adagrad", max_keys_per_batch=1 << 19, world_size=8, dense_params=600_000)
+    assert b.fits() and 15e9 < b.table_bytes < 40e9 and b.engine_bytes < 2e9
+    assert "GB HBM" in b.report()
+    # the same table at dim 64 with per-element Adam state does not fit a 180 GB device any more at 450 M keys
+    big = plan(450_000_000, 64, "adam", max_keys_per_batch=1 << 22, world_size=8)
+    assert not big.fits() and big.hbm_bytes > 180e9
+    one = plan(1000, 8, world_size=1, max_keys_per_batch=4096)
+    assert one.mailbox_cap == 4096 and one.table_capacity == 1334
