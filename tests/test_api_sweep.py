@@ -552,3 +552,23 @@ def test_capacity_planner_for_the_headline_config():
     assert not big.fits() and big.hbm_bytes > 180e9
     one = plan(1000, 8, world_size=1, max_keys_per_batch=4096)
     assert one.mailbox_cap == 4096 and one.table_capacity == 1334
+
+
+def test_lod_tensor_bytes_are_the_reference_layout():
+    """Byte-exact check of the serialized LoDTensor (lod_tensor.cc:205-231, tensor_util.cc:1056-1110), hand
+    assembled: u32 0 | u64 lod levels | u32 0 | i32 desc size | TensorDesc{data_type=FP32(5), dims} | data."""
+    import struct
+    from paddlebox_b200.checkpoint import deserialize_lod_tensor, serialize_lod_tensor
+    t = torch.tensor([[1.0, 2.0]])
+    desc = bytes([0x08, 0x05, 0x10, 0x01, 0x10, 0x02])
+    want = struct.pack("<IQ", 0, 0) + struct.pack("<Ii", 0, len(desc)) + desc + struct.pack("<2f", 1.0, 2.0)
+    assert serialize_lod_tensor(t) == want
+    back = deserialize_lod_tensor(want)
+    got = back[0] if isinstance(back, tuple) else back
+    assert torch.equal(torch.as_tensor(got).reshape(1, 2), t)
+    # one LoD level [0, 2, 3]: u64 byte size (24) then the three u64 offsets
+    t3 = torch.arange(3, dtype=torch.int64)
+    raw = serialize_lod_tensor(t3, lod=[[0, 2, 3]])
+    head = struct.pack("<IQ", 0, 1) + struct.pack("<Q3Q", 24, 0, 2, 3)
+    desc3 = bytes([0x08, 0x03, 0x10, 0x03])
+    assert raw == head + struct.pack("<Ii", 0, len(desc3)) + desc3 + struct.pack("<3q", 0, 1, 2)
