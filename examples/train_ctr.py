@@ -26,6 +26,8 @@ from paddlebox_b200.data_generator import format_instance               # noqa: 
 from paddlebox_b200.dataset import DatasetFactory, dense_slot, sparse_slot   # noqa: E402
 from paddlebox_b200.models.ctr import build_model                       # noqa: E402
 from paddlebox_b200.trainer import CTRTrainer, TrainerConfig            # noqa: E402
+from paddlebox_b200.checkpoint import save_persistables                 # noqa: E402
+from paddlebox_b200.utils.donefile import ModelManifest                 # noqa: E402
 
 
 def write_pass_files(directory: str, n_files: int, lines: int, n_sparse: int, n_dense: int, seed: int,
@@ -90,6 +92,7 @@ def main():
     data_dir = os.path.join(out, "data")
     os.makedirs(data_dir, exist_ok=True)
     ds.set_date("20240101")
+    manifest = ModelManifest(os.path.join(out, "donefiles"))        # what serving and a restarted job read
     aucs = []
     for p in range(a.passes):
         files = write_pass_files(data_dir, n_files=2 * world, lines=a.lines, n_sparse=a.slots, n_dense=a.dense, seed=p,
@@ -101,6 +104,9 @@ def main():
         stats = trainer.train_from_dataset(ds)
         ds.end_pass(False)                # HBM -> host tier
         box.save_delta(os.path.join(out, f"xbox_delta_{p}"))
+        if rank == 0:
+            save_persistables(model, os.path.join(out, f"dense_{p}"))
+            manifest.record_delta("20240101", p, os.path.join(out, f"xbox_delta_{p}"), os.path.join(out, f"dense_{p}"))
         msg = box.get_metric_msg("auc")
         aucs.append(msg[0])
         if rank == 0:
@@ -110,6 +116,9 @@ def main():
     kept = box.shrink_table(decay=0.98, delete_threshold=0.0, delete_after_unseen_days=30)
     info = box.save_base(os.path.join(out, "batch_model"), os.path.join(out, "xbox_base"), "20240101")
     if rank == 0:
+        save_persistables(model, os.path.join(out, "dense_base"))
+        manifest.record_base("20240101", os.path.join(out, "xbox_base"), os.path.join(out, "batch_model"),
+                             os.path.join(out, "dense_base"), pass_id=a.passes)
         print(f"day end: {kept} rows kept, {info}; models under {out}")
         print(box.print_sync_timer())
     return aucs

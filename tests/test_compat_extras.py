@@ -424,6 +424,12 @@ def test_examples_run_on_cpu(tmp_path):
     aucs = [float(ln.split("auc ")[1].split()[0]) for ln in lines]
     assert aucs[-1] > aucs[0] and aucs[-1] > 0.58, aucs
     assert os.path.isdir(tmp_path / "batch_model") and os.path.isdir(tmp_path / "xbox_base")
+    assert os.path.exists(tmp_path / "donefiles" / "xbox_base_done.txt") and os.path.isdir(tmp_path / "dense_base")
+    r = subprocess.run([sys.executable, os.path.join(root, "examples", "serve.py"), "--cpu", "--job", str(tmp_path)],
+                       capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    preds = [float(v) for v in r.stdout.split("predictions:")[1].split()]
+    assert len(preds) == 16 and all(0.0 < v < 1.0 for v in preds) and len(set(preds)) > 1
     r = subprocess.run([sys.executable, os.path.join(root, "examples", "graph_skipgram.py"), "--cpu", "--epochs", "3"],
                        capture_output=True, text=True, env=env, timeout=600)
     assert r.returncode == 0, r.stdout + r.stderr
