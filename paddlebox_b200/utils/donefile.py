@@ -29,10 +29,9 @@ class ModelManifest:
     # ---- writing -------------------------------------------------------------------------------
     def _append(self, name: str, entry: dict) -> dict:
         path = os.path.join(self.root, name)
-        old = ""
-        if os.path.exists(path):
-            with open(path) as f:
-                old = f.read()
+        # keep the complete, parsable lines only: a torn tail left by a crashed writer must not swallow the
+        # new entry
+        old = "".join(json.dumps(e, sort_keys=True) + "\n" for e in self._read(name))
         tmp = path + ".tmp"
         with open(tmp, "w") as f:
             f.write(old + json.dumps(entry, sort_keys=True) + "\n")
@@ -85,10 +84,12 @@ class ModelManifest:
         return base, deltas
 
 
-def resume(box, manifest: ModelManifest, serving: bool = False) -> dict:
+def resume(box, manifest: ModelManifest, serving: bool = False, model=None) -> dict:
     """Load the newest base (its batch model when there is one and ``serving`` is False, else the xbox
     base) and every later delta into ``box``; returns what was loaded.  Deltas are serving-format rows:
-    weights and show / click are restored, optimizer state of those rows restarts."""
+    weights and show / click are restored, optimizer state of those rows restarts.  With ``model`` the dense
+    parameters recorded with the newest entry (``dense`` directory, ``checkpoint.save_persistables`` layout)
+    are loaded into it as well."""
     base, deltas = manifest.latest()
     loaded = {"base": None, "deltas": [], "rows": 0}
     if base is not None:
@@ -101,4 +102,14 @@ def resume(box, manifest: ModelManifest, serving: bool = False) -> dict:
         loaded["deltas"].append(d["input"])
     if base is not None and base.get("day"):
         box.set_date(base["day"])
+    if model is not None:
+        newest = (deltas[-1] if deltas else base) or {}
+        dense_dir = newest.get("dense") or (base or {}).get("dense")
+        if dense_dir and os.path.isdir(dense_dir):
+            from ..checkpoint import load_persistables
+            load_persistables(model, dense_dir, strict=False)
+            fn = getattr(model, "mark_weights_dirty", None)
+            if fn:
+                fn()
+            loaded["dense"] = dense_dir
     return loaded

@@ -309,6 +309,19 @@ def test_donefile_manifest_and_resume(tmp_path, box):
     b3.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0})
     assert resume(b3, man, serving=True)["base"].endswith("xbox")
     assert torch.allclose(b3.host_table.pull(keys), want, atol=1e-6)
+    # dense parameters travel with the manifest entries
+    from paddlebox_b200.checkpoint import save_persistables
+    from paddlebox_b200.models.ctr import CtrDnn
+    torch.manual_seed(1)
+    m1 = CtrDnn(num_slots=2, embedx_dim=4, dense_dim=1, hidden=(4,))
+    save_persistables(m1, str(tmp_path / "dense3"))
+    man.record_delta("20240102", 3, str(tmp_path / "d2"), str(tmp_path / "dense3"))
+    torch.manual_seed(2)
+    m2 = CtrDnn(num_slots=2, embedx_dim=4, dense_dim=1, hidden=(4,))
+    got = resume(b3, man, serving=True, model=m2)
+    assert got["dense"].endswith("dense3")
+    for (n1, p1), (n2, p2) in zip(m1.named_dense_params(), m2.named_dense_params()):
+        assert n1 == n2 and torch.equal(p1, p2)
 
 
 def test_fused_seqpool_concat_two_groups():
