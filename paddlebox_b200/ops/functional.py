@@ -88,6 +88,39 @@ class _DataNorm(torch.autograd.Function):
         return dx, None, None, None, None, None
 
 
+class _DataNormSlot(torch.autograd.Function):
+    """data_norm with ``slot_dim``: the input row is a run of slot blocks of ``slot_dim`` columns whose first
+    column is the slot's show count; a block with show == 0 (|x| < 1e-7) yields zeros, receives no gradient
+    and does not count in the batch statistics (CPU kernels data_norm_op.cc:334-362, :592-720).  Returns
+    ``(y, mask)``."""
+
+    @staticmethod
+    def forward(ctx, x, bsize, bsum, bsq, eps, stat_sink, slot_dim):
+        rows, Cc = x.shape
+        mean = bsum / bsize
+        scale = torch.sqrt(bsize / bsq)
+        show = x.reshape(rows, Cc // slot_dim, slot_dim)[:, :, 0]
+        live = (show.abs() >= 1e-7)                                            # [rows, blocks]
+        mask = live[:, :, None].expand(rows, Cc // slot_dim, slot_dim).reshape(rows, Cc).to(x.dtype)
+        y = (x - mean) * scale * mask
+        ctx.save_for_backward(x, mask, mean, scale)
+        ctx.eps, ctx.sink = eps, stat_sink
+        ctx.mark_non_differentiable(mask)
+        return y, mask
+
+    @staticmethod
+    def backward(ctx, dy, _dmask):
+        x, mask, mean, scale = ctx.saved_tensors
+        if ctx.sink is not None:
+            cnt = mask.sum(0)
+            has = (cnt >= 1).to(x.dtype)
+            denom = cnt.clamp(min=1.0)
+            d_sum = (x * mask).sum(0) / denom * has
+            d_sq = ((((x - mean) ** 2) * mask).sum(0) / denom + cnt * ctx.eps) * has
+            ctx.sink(has, d_sum, d_sq)
+        return dy * scale * mask, None, None, None, None, None, None
+
+
 class DataNorm(nn.Module):
     """``y = (x - batch_sum/batch_size) * sqrt(batch_size/batch_square_sum)``.
 
@@ -98,12 +131,22 @@ class DataNorm(nn.Module):
     (reference: 3 ncclAllReduce calls, data_norm_op.cu:203-231)."""
 
     def __init__(self, num_features: int, epsilon: float = 1e-4, summary_decay_rate: float = 0.9999999,
-                 sync_stats: bool = False, name: str = "data_norm"):
+                 sync_stats: bool = False, name: str = "data_norm", slot_dim: int = -1,
+                 enable_scale_and_shift: bool = False):
+        """``slot_dim`` > 0: show-aware normalisation per slot block (see ``_DataNormSlot``);
+        ``enable_scale_and_shift``: trainable ``scale_w`` / ``bias`` applied after the normalisation
+        (``y * scale_w + bias``; data_norm_op.cc:369-386) — both are options of the reference layer
+        (layers/nn.py:3490-3504)."""
         super().__init__()
         self.name = name
         self.epsilon = epsilon
         self.decay = summary_decay_rate
         self.sync_stats = sync_stats
+        self.slot_dim = slot_dim
+        if slot_dim > 0 and num_features % slot_dim:
+            raise ValueError(f"num_features {num_features} is not a multiple of slot_dim {slot_dim}")
+        self.scale_w = nn.Parameter(torch.ones(num_features)) if enable_scale_and_shift else None
+        self.bias = nn.Parameter(torch.zeros(num_features)) if enable_scale_and_shift else None
         self.register_buffer("batch_size", torch.full((num_features,), 1e4))
         self.register_buffer("batch_sum", torch.zeros(num_features))
         self.register_buffer("batch_square_sum", torch.full((num_features,), 1e4))
@@ -120,7 +163,12 @@ class DataNorm(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         sink = self._apply_stats if self.training else None
-        return _DataNorm.apply(x, self.batch_size, self.batch_sum, self.batch_square_sum, self.epsilon, sink)
+        if self.slot_dim > 0:
+            y, mask = _DataNormSlot.apply(x, self.batch_size, self.batch_sum, self.batch_square_sum, self.epsilon,
+                                          sink, self.slot_dim)
+            return y if self.scale_w is None else (y * self.scale_w + self.bias) * mask
+        y = _DataNorm.apply(x, self.batch_size, self.batch_sum, self.batch_square_sum, self.epsilon, sink)
+        return y if self.scale_w is None else y * self.scale_w + self.bias
 
 
 def data_norm(x, batch_size, batch_sum, batch_square_sum, epsilon: float = 1e-4, stat_sink=None):

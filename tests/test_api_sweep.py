@@ -585,3 +585,44 @@ def test_lod_tensor_bytes_are_the_reference_layout():
     head = struct.pack("<IQ", 0, 1) + struct.pack("<Q3Q", 24, 0, 2, 3)
     desc3 = bytes([0x08, 0x03, 0x10, 0x03])
     assert raw == head + struct.pack("<Ii", 0, len(desc3)) + desc3 + struct.pack("<3q", 0, 1, 2)
+
+
+def test_data_norm_slot_dim_and_scale_shift():
+    from paddlebox_b200.ops.functional import DataNorm
+    torch.manual_seed(0)
+    x = torch.rand(6, 8) + 0.5
+    x[1, 0] = 0.0                                   # slot block 0 of row 1 has show == 0
+    x[4, 4] = 0.0                                   # slot block 1 of row 4
+    dn = DataNorm(8, slot_dim=4, enable_scale_and_shift=True)
+    with torch.no_grad():
+        dn.batch_sum.fill_(5e3)                      # mean 0.5, scale 1
+        dn.scale_w.copy_(torch.arange(1., 9.))
+        dn.bias.fill_(0.25)
+    xr = x.clone().requires_grad_(True)
+    y = dn(xr)
+    want = ((x - 0.5) * torch.arange(1., 9.) + 0.25)
+    want[1, :4] = 0
+    want[4, 4:] = 0
+    assert torch.allclose(y, want, atol=1e-6)
+    size0, sum0, sq0 = dn.batch_size.clone(), dn.batch_sum.clone(), dn.batch_square_sum.clone()
+    y.sum().backward()
+    g = torch.arange(1., 9.).repeat(6, 1)
+    g[1, :4] = 0
+    g[4, 4:] = 0
+    assert torch.allclose(xr.grad, g)
+    live = torch.ones(6, 8)
+    live[1, :4] = 0
+    live[4, 4:] = 0
+    assert torch.allclose(dn.bias.grad, live.sum(0)) and torch.allclose(dn.scale_w.grad, ((x - 0.5) * live).sum(0), atol=1e-5)
+    # summaries: +1 per column, mean / mean-square of the live rows only (+ count * eps)
+    cnt = live.sum(0)
+    assert torch.allclose(dn.batch_size, size0 * dn.decay + 1)
+    assert torch.allclose(dn.batch_sum, sum0 * dn.decay + (x * live).sum(0) / cnt, rtol=1e-6)
+    assert torch.allclose(dn.batch_square_sum, sq0 * dn.decay + (((x - 0.5) ** 2) * live).sum(0) / cnt + cnt * dn.epsilon, rtol=1e-6)
+    # plain layer with scale and shift only
+    d2 = DataNorm(8, enable_scale_and_shift=True)
+    with torch.no_grad():
+        d2.scale_w.fill_(2.0); d2.bias.fill_(1.0)
+    assert torch.allclose(d2(x), x * 2 + 1, atol=1e-5)           # mean 0, scale 1 at initialisation
+    with pytest.raises(ValueError):
+        DataNorm(7, slot_dim=4)
