@@ -426,3 +426,26 @@ def cpu_reshard_on_load(rank, world, ckpt):
     box.save_base(out)
     dist.barrier()
     return int(tot)
+
+
+def cpu_one_rank_per_node(rank, world):
+    """Every rank is its own node (gpus_per_node = 1): the intra-node legs are trivial, the inter-node leg
+    carries the whole buffer."""
+    from paddlebox_b200.parallel.dense import DenseOptimizer, DenseParamStore, DenseSync
+    from paddlebox_b200.parallel.topology import NodeTopology
+    topo = NodeTopology(gpus_per_node=1)
+    assert (topo.nnodes, topo.local_size, topo.local_rank, topo.node_rank) == (world, 1, 0, rank)
+    x = torch.arange(10.) * (rank + 1)
+    topo.hierarchical_allreduce(x, 1.0 / world)
+    assert torch.allclose(x, torch.arange(10.) * sum(range(1, world + 1)) / world)
+    torch.manual_seed(0)
+    model = torch.nn.Linear(4, 2)
+    store = DenseParamStore(model, rank, world, topo=topo)
+    for mode in ("allreduce", "sharding"):
+        sync = DenseSync(store, DenseOptimizer(store, lr=0.1, kind="sgd"), mode)
+        model(torch.full((3, 4), float(rank + 1))).sum().backward()
+        sync.after_backward()
+        gathered = [torch.zeros_like(store.flat) for _ in range(world)]
+        dist.all_gather(gathered, store.flat)
+        assert all(torch.allclose(gathered[0], t) for t in gathered), mode
+    return True
