@@ -449,3 +449,38 @@ def cpu_one_rank_per_node(rank, world):
         dist.all_gather(gathered, store.flat)
         assert all(torch.allclose(gathered[0], t) for t in gathered), mode
     return True
+
+
+def cpu_router_edge_cases(rank, world):
+    """One rank with no keys at all, heavy duplicates, the padding key 0, and keys nobody registered."""
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=rank, world_size=world)
+    box.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0})
+    mine = torch.tensor([7, 7, 7, 0, 9, 7], dtype=torch.int64) if rank == 1 else torch.zeros(0, dtype=torch.int64)
+    box.begin_feed_pass("20240101")
+    box.feed_pass(mine)
+    box.end_feed_pass()
+    box.begin_pass()
+    keys = torch.cat([mine, torch.tensor([12345], dtype=torch.int64)]) if rank == 1 else mine   # 12345 was never fed
+    vals, restore = box.pull_sparse(keys)
+    assert restore.numel() == keys.numel() and vals.shape[1] == box.hidden
+    if rank == 1:
+        got = vals[restore.long()]
+        assert torch.all(got[3] == 0) and torch.all(got[6] == 0)           # key 0 and the unknown key pull zeros
+        assert torch.equal(got[0], got[1]) and torch.equal(got[0], got[5])
+    grads = torch.zeros(keys.numel(), box.hidden)
+    grads[:, 0] = 1.0
+    box.push_sparse_grad(keys, restore, grads, torch.zeros(keys.numel(), dtype=torch.int32), 4)
+    dist.barrier()
+    box.end_pass()
+    total = torch.tensor([box.host_table.size()])
+    dist.all_reduce(total)
+    shows = 0.0
+    ks = box.host_table.keys()
+    if ks.size:
+        shows = float(box.host_table.fetch_rows(ks, create=False)[:, 0].sum())
+    s = torch.tensor([shows])
+    dist.all_reduce(s)
+    # keys 0 (registered by both ranks' feed pass on its owner), 7, 9 exist; 12345 was not created by the push
+    assert int(total) in (3, 4) and abs(float(s) - 5.0) < 1e-5, (int(total), float(s))
+    return True

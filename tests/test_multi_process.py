@@ -88,6 +88,10 @@ def test_model_saved_by_one_rank_loads_into_three_and_back(tmp_path):
     assert np.allclose(t2.fetch_rows(keys, create=False), t.fetch_rows(keys, create=False), rtol=1e-6)
 
 
+def test_sparse_router_edge_cases_gloo():
+    assert all(_spawn(W.cpu_router_edge_cases, 2, "gloo"))
+
+
 def test_one_rank_per_node_topology_gloo():
     assert all(_spawn(W.cpu_one_rank_per_node, 3, "gloo"))
 
