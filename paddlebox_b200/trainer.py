@@ -73,6 +73,8 @@ class CTRTrainer:
             self.store.broadcast_params(0)
             self.store.mark_dirty()
         self.pinned_cores = self._bind_train_cpu()
+        if FLAGS.enable_dump_main_program:
+            self.dump_main_program()
         self.timers = CudaStageTimers(self.cfg.debug)
         self.dumper = None
         if self.cfg.dump_fields_path and (self.cfg.dump_fields or self.cfg.dump_param):
@@ -84,6 +86,27 @@ class CTRTrainer:
         for m in model.modules():
             if getattr(m, "sync_stats", False) and self.world > 1:
                 m.reduce_fn = self._reduce_stats
+
+    def dump_main_program(self, path: str | None = None) -> str:
+        """``FLAGS_enable_dump_main_program``: the reference writes every device's op list to
+        ``./device_<id>_ops.txt`` (boxps_worker.cc:860-880).  There is no op list here — the step is autograd plus
+        one CUDA graph — so the file holds what plays that role: the module tree, every dense parameter with its
+        checkpoint name, shape and offset in the flat buffer, the sparse table and the sync configuration."""
+        path = path or f"./device_{self.rank}_ops.txt"
+        named = dict((id(p), n) for n, p in (self.model.named_dense_params() if hasattr(self.model, "named_dense_params")
+                                             else self.model.named_parameters()))
+        lines = [f"# device {self.rank} of {self.world}: dense sync {self.sync.mode}, optimizer {self.opt.kind} lr {self.opt.lr}",
+                 f"# sparse table: embedx_dim {self.box.embedx_dim}, optimizer {self.box.optimizer}, "
+                 f"feature_type {self.box.feature_type}, hidden {self.box.hidden}", "", "[modules]"]
+        for name, mod in self.model.named_modules():
+            lines.append(f"{name or '<root>'}: {type(mod).__name__}")
+        lines += ["", "[dense parameters]  name shape flat_offset"]
+        for p, off in zip(self.store.params, self.store.offsets):
+            lines.append(f"{named.get(id(p), '?')} {tuple(p.shape)} {off}")
+        lines.append(f"# flat buffer: {self.store.numel} floats, symmetric memory {bool(self.store.use_symm)}")
+        with open(path, "w") as f:
+            f.write("\n".join(lines) + "\n")
+        return path
 
     def _bind_train_cpu(self) -> list:
         """FLAGS_enable_binding_train_cpu (boxps_trainer.cc:165-193): the training thread of this process is

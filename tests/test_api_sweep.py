@@ -626,3 +626,18 @@ def test_data_norm_slot_dim_and_scale_shift():
     assert torch.allclose(d2(x), x * 2 + 1, atol=1e-5)           # mean 0, scale 1 at initialisation
     with pytest.raises(ValueError):
         DataNorm(7, slot_dim=4)
+
+
+def test_dump_main_program(tmp_path, box, monkeypatch):
+    from paddlebox_b200.flags import FLAGS
+    from paddlebox_b200.models.ctr import DeepFM
+    from paddlebox_b200.trainer import CTRTrainer
+    monkeypatch.chdir(tmp_path)
+    FLAGS.enable_dump_main_program = True
+    try:
+        tr = CTRTrainer(DeepFM(num_slots=2, embedx_dim=4, dense_dim=1, hidden=(4,)), box)
+    finally:
+        FLAGS.enable_dump_main_program = False
+    text = (tmp_path / "device_0_ops.txt").read_text()
+    assert "[modules]" in text and "DeepFM" in text and "fc_0.w_0" in text and "dense sync" in text
+    assert tr.dump_main_program(str(tmp_path / "again.txt")).endswith("again.txt")
