@@ -72,6 +72,8 @@ class DatasetBase:
         self.fs_name = self.fs_ugi = ""
         self.download_cmd = "cat"
         self.trainer_num = 1
+        # FLAGS_padbox_dataset_merge_thread_num (default 20 in the reference): capped by the cores there are
+        self._native.set("merge_thread_num", max(1, min(FLAGS.padbox_dataset_merge_thread_num, os.cpu_count() or 1, 8)))
         self._prepared_workers = 0
         self._device = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() \
             else torch.device("cpu")

@@ -85,6 +85,10 @@ class MetricMsg:
         self._reduce(group)
         out = self.calc.compute()
         self.calc.reset()
+        from .flags import FLAGS
+        if FLAGS.enable_debug_print_metrics_info:          # verbose AUC computation (metrics.cc:29-31)
+            names = ("auc", "bucket_error", "mae", "rmse", "actual_ctr", "predicted_ctr", "copc", "size")
+            print(f"[metric {self.name}] " + " ".join(f"{n}={v:.6g}" for n, v in zip(names, out)), flush=True)
         return out
 
     def get_nan_inf_msg(self) -> list:

@@ -261,6 +261,9 @@ class DenseSync:
     def after_backward(self) -> None:
         s, o = self.store, self.opt
         self.steps += 1
+        if FLAGS.enable_dense_nccl_barrier and s.nranks > 1 and self.mode in ("allreduce", "kstep", "sharding"):
+            import torch.distributed as dist                # FLAGS_enable_dense_nccl_barrier: ranks meet first
+            dist.barrier(group=s.group)
         if self.mode == "none":
             o.step()
         elif self.mode == "allreduce":

@@ -24,7 +24,10 @@ from .ops.functional import row_gather
 
 
 class GpuReplicaCache:
-    def __init__(self, emb_dim: int = 8):
+    def __init__(self, emb_dim: int | None = None):
+        if emb_dim is None:
+            from .flags import FLAGS
+            emb_dim = FLAGS.gpu_replica_cache_dim       # FLAGS_gpu_replica_cache_dim (flags.cc)
         self.emb_dim = emb_dim
         self._host: list = []
         self._lock = threading.Lock()

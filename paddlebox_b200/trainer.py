@@ -136,7 +136,8 @@ class CTRTrainer:
         read the real key count from the device (``lod[S*B]``).  The ``warmup`` eager steps and
         the capture run are real training steps on ``example_batch``.  Returns False (and stays
         eager) when capture is not possible on this setup."""
-        if not example_batch.keys.is_cuda or self.cfg.is_test or self.sync.mode == "async":
+        if not example_batch.keys.is_cuda or self.cfg.is_test or self.sync.mode == "async" \
+                or not FLAGS.pbx_use_cuda_graph:
             return False
         from .ops.pull_box_sparse import SlotBatch
         B, S = example_batch.batch_size, example_batch.num_slots
@@ -218,6 +219,8 @@ class CTRTrainer:
 
     def _eager_step(self, batch) -> torch.Tensor:
         t = self.timers
+        if FLAGS.padbox_enable_print_op_debug:              # one line per stage (boxps_worker.cc:50-52)
+            print(f"[rank {self.rank} step {self.steps}] forward B={batch.batch_size} keys={batch.N}", flush=True)
         self.sync.before_forward()
         with t.span("forward"):
             loss, outs = self.model(batch)

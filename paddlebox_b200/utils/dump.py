@@ -50,6 +50,9 @@ class FieldDumper:
             self._q.task_done()
 
     def _keep(self, lineid: str) -> bool:
+        from ..flags import FLAGS
+        if FLAGS.padbox_dump_debug_lineid:                  # debug: only this line id (boxps_worker.cc:47-49)
+            return lineid == FLAGS.padbox_dump_debug_lineid
         if self.mode == 0:
             return True
         if self.mode == 1:

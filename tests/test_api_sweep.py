@@ -641,3 +641,27 @@ def test_dump_main_program(tmp_path, box, monkeypatch):
     text = (tmp_path / "device_0_ops.txt").read_text()
     assert "[modules]" in text and "DeepFM" in text and "fc_0.w_0" in text and "dense sync" in text
     assert tr.dump_main_program(str(tmp_path / "again.txt")).endswith("again.txt")
+
+
+def test_debug_flags_are_wired(tmp_path, box, capsys):
+    from paddlebox_b200.flags import FLAGS
+    from paddlebox_b200.side_tables import GpuReplicaCache
+    from paddlebox_b200.utils.dump import FieldDumper
+    box.init_metric("AucCalculator", "m", "label", "pred", metric_phase=1, bucket_size=100)
+    box.add_metric_data({"pred": torch.tensor([0.2, 0.9]), "label": torch.tensor([0., 1.])})
+    FLAGS.enable_debug_print_metrics_info = True
+    FLAGS.padbox_dump_debug_lineid = "ins_b"
+    FLAGS.gpu_replica_cache_dim = 3
+    try:
+        box.get_metric_msg("m")
+        assert "[metric m] auc=1" in capsys.readouterr().out
+        d = FieldDumper(str(tmp_path / "dump"), ["pred"])
+        d.dump_batch(["ins_a", "ins_b"], {"pred": torch.tensor([0.1, 0.7])})
+        d.close()
+        text = "".join(open(os.path.join(tmp_path / "dump", f)).read() for f in os.listdir(tmp_path / "dump"))
+        assert "ins_b" in text and "ins_a" not in text
+        assert GpuReplicaCache().emb_dim == 3
+    finally:
+        FLAGS.enable_debug_print_metrics_info = False
+        FLAGS.padbox_dump_debug_lineid = ""
+        FLAGS.gpu_replica_cache_dim = 8
