@@ -53,13 +53,13 @@ FLAGS = _Flags()
 _d = FLAGS.define
 
 # --- pull / push -------------------------------------------------------------
-_d("enable_pullpush_dedup_keys", True, "dedup keys before pull/push (flags.cc:946)")
+_d("enable_pullpush_dedup_keys", True, "dedup keys before pull/push (flags.cc:946); always on here: the pull kernel dedups in its first phase")
 _d("enable_pull_box_padding_zero", True, "empty slot -> one zero row (pull_box_sparse_op.h:131-147)")
 _d("gpugraph_hbm_table_load_factor", 0.75, "max load factor of the HBM table")
 _d("gpugraph_enable_gpu_direct_access", True, "owner writes requester buffers through peer pointers (always on here)")
-_d("gpugraph_enable_segment_merge_grads", False, "two-level gradient merge for hot keys")
-_d("gpugraph_merge_grads_segment_size", 128, "segment size of the two-level merge")
-_d("gpugraph_dedup_pull_push_mode", 1, "dedup mode")
+_d("gpugraph_enable_segment_merge_grads", False, "two-level gradient merge for hot keys; accepted, not needed: the push merges with vector atomics into the unique row")
+_d("gpugraph_merge_grads_segment_size", 128, "segment size of the two-level merge (see gpugraph_enable_segment_merge_grads)")
+_d("gpugraph_dedup_pull_push_mode", 1, "dedup mode; one mode here (hash dedup inside the pull kernel, restore index reused by the push)")
 # --- dense sync ------------------------------------------------------------------
 _d("enable_sync_dense_moment", False, "also average Adam moments in K-step sync (boxps_worker.cc:468-475)")
 _d("enable_dense_nccl_barrier", False, "barrier before dense sync")
@@ -69,19 +69,19 @@ _d("dense_use_nccl", False, "use the NCCL baseline path instead of the symmetric
 _d("enable_binding_train_cpu", True, "pin worker threads to cores (boxps_trainer.cc:165-193)")
 _d("enable_shuffle_by_searchid", False, "hash records by search_id in global shuffle")
 _d("enable_ins_parser_file", False, "parser plugin consumes whole files")
-_d("padbox_record_pool_max_size", 2000000, "SlotRecord object pool cap (data_feed.h:241-428)")
-_d("padbox_slotrecord_extend_dim", 0, "extra floats appended to each record")
-_d("padbox_dataset_shuffle_thread_num", 20, "shuffle threads")
+_d("padbox_record_pool_max_size", 2000000, "SlotRecord object pool cap (data_feed.h:241-428); the native pool frees on release_memory")
+_d("padbox_slotrecord_extend_dim", 0, "extra floats appended to each record; accepted, records carry no trailing block here")
+_d("padbox_dataset_shuffle_thread_num", 20, "shuffle threads; the network shuffle is one all-to-all, the partition runs on the dataset's threads")
 _d("padbox_dataset_merge_thread_num", 20, "merge / key-collection threads")
 _d("padbox_dataset_disable_shuffle", False, "skip cross-node shuffle")
 _d("padbox_dataset_disable_polling", False, "round-robin file assignment instead of polling")
 _d("padbox_disable_ins_shuffle", False, "keep instance order in PrepareTrain (data_set.cc:42)")
 _d("padbox_auc_runner_mode", False, "slot-shuffle feature evaluation mode")
-_d("use_gpu_replica_cache", False, "enable GpuReplicaCache")
+_d("use_gpu_replica_cache", False, "enable GpuReplicaCache; the cache object (side_tables.GpuReplicaCache) is created by the user script")
 _d("gpu_replica_cache_dim", 8, "row width of the replica cache")
 _d("fix_dayid", False, "do not advance the day id between passes")
 # --- worker -----------------------------------------------------------------------
-_d("padbox_enable_gc", True, "eager free of dead activations")
+_d("padbox_enable_gc", True, "eager free of dead activations; PyTorch autograd frees them, the captured step reuses static buffers")
 _d("padbox_enable_print_op_debug", False, "log every op before it runs")
 _d("padbox_dump_debug_lineid", "", "dump only this line id")
 _d("enable_dump_main_program", False, "write the per-device op list to ./device_<id>_ops.txt")
