@@ -610,3 +610,17 @@ def test_native_util_selftest(tmp_path):
                            os.path.join(root, "csrc", "host", "tests", "util_selftest.cc")])
     r = subprocess.run([str(exe)], capture_output=True, text=True, timeout=120)
     assert r.returncode == 0 and "util selftest ok" in r.stdout, r.stdout + r.stderr
+
+
+@pytest.mark.skipif(not os.environ.get("PBX_RUN_SANITIZERS"), reason="set PBX_RUN_SANITIZERS=1 (two sanitizer builds, ~2 min)")
+def test_host_runtime_under_sanitizers(tmp_path):
+    """ASan + UBSan and TSan builds of csrc/host driven through the C ABI (benchmarks/sanitize_host.sh); the
+    committed logs of the same run are profiles/sanitizer_host_{asan,tsan}.log."""
+    import subprocess
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([os.path.join(root, "benchmarks", "sanitize_host.sh"), str(tmp_path)], capture_output=True,
+                       text=True, timeout=1200)
+    assert r.returncode == 0, r.stdout + r.stderr
+    for mode in ("asan", "tsan"):
+        log = (tmp_path / f"sanitizer_host_{mode}.log").read_text()
+        assert "exit code 0" in log and "WARNING" not in log and "ERROR" not in log, log
