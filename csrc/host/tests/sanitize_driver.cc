@@ -172,6 +172,45 @@ int main(int argc, char** argv) {
   int64_t counts[5];
   OK(pbh_partition_by_owner(copy.data(), nu, 5, parted.data(), counts));
   CHECK(counts[0] + counts[1] + counts[2] + counts[3] + counts[4] == nu);
+  // text parser on hostile input: random bytes, truncated numbers, huge counts, embedded NULs, very long lines
+  {
+    const std::string junk = dir + "/san-junk.txt";
+    FILE* fp = fopen(junk.c_str(), "w");
+    CHECK(fp != nullptr);
+    const char* seeds[] = {"1 1.0 3 0.5 0.25 0.1 1 7 1 8 1 9 1 10 1 11 1 12", "1", "1 ", "999999999999 1", "1 1.0 3 0.5",
+                           "1 1.0 3 0.5 0.25 0.1 18446744073709551615 1", "1 1e400 3 nan inf -inf 2 1 2", "-1 -1 -1 -1",
+                           "1 1.0 3 0.5 0.25 0.1 1 99999999999999999999999999 1 8 1 9 1 10 1 11 1 12", "\t\t \t"};
+    for (int rep = 0; rep < 400; ++rep) {
+      std::string line = seeds[rnd() % 10];
+      int edits = rnd() % 4;
+      for (int e = 0; e < edits && !line.empty(); ++e) {
+        size_t pos = rnd() % line.size();
+        switch (rnd() % 4) {
+          case 0: line[pos] = (char)(rnd() & 0xff); if (line[pos] == '\n') line[pos] = ' '; break;
+          case 1: line.erase(pos); break;
+          case 2: line.insert(pos, std::string(1 + rnd() % 40, (char)('0' + rnd() % 10))); break;
+          default: line.insert(pos, " "); break;
+        }
+      }
+      fwrite(line.data(), 1, line.size(), fp);
+      fputc('\n', fp);
+    }
+    std::string longline(300000, '7');
+    fprintf(fp, "1 1.0 3 0.5 0.25 0.1 1 %s 1 8 1 9 1 10 1 11 1 12\n", longline.c_str());
+    fclose(fp);
+    void* dj = make_dataset(S);
+    const char* jf[1] = {junk.c_str()};
+    OK(pbh_dataset_set_filelist(dj, 1, jf));
+    OK(pbh_dataset_set_int(dj, "thread_num", 2));
+    OK(pbh_dataset_set_int(dj, "parse_ins_id", 0));
+    OK(pbh_dataset_load_into_memory(dj));
+    CHECK(pbh_dataset_num_records(dj) >= 0);
+    OK(pbh_dataset_set_int(dj, "parse_ins_id", 1));          // same bytes, now with the id / logkey groups expected
+    OK(pbh_dataset_set_int(dj, "parse_logkey", 1));
+    OK(pbh_dataset_load_into_memory(dj));
+    OK(pbh_dataset_prepare_train(dj, 2, 1, 1, 0));
+    OK(pbh_dataset_destroy(dj));
+  }
   // graph store: build, threaded sampling and walks
   {
     void* g = nullptr;
