@@ -892,6 +892,32 @@ int Dataset::load_arena(const std::string& path) {
                 path.c_str(), fs, fd_, n_used_u64_, dense_dim_);
   }
   const char* b = (const char*)base;
+  {
+    // the header only says where things are: every section must lie inside the file and the offsets must be
+    // what build_arena writes (a damaged file is refused here instead of being read out of bounds later)
+    const int64_t fsz = (int64_t)st.st_size, S1 = (int64_t)h.S + 1;
+    auto inside = [&](int64_t off, int64_t bytes) { return off >= (int64_t)sizeof(ArenaHeader) && bytes >= 0 && off <= fsz && bytes <= fsz - off; };
+    bool ok = h.n <= (int64_t)1 << 40 && h.nkeys <= (int64_t)1 << 44 && h.n_unique <= (int64_t)1 << 44 &&
+              inside(h.off_koff, (h.n + 1) * 8) && inside(h.off_soff, h.n * S1 * 4) &&
+              inside(h.off_dense, h.n * (int64_t)h.dense_dim * 4) && inside(h.off_keys, h.nkeys * 8) &&
+              inside(h.off_unique, h.n_unique * 8) && h.off_koff % 8 == 0 && h.off_soff % 4 == 0 &&
+              h.off_dense % 4 == 0 && h.off_keys % 8 == 0 && h.off_unique % 8 == 0;
+    if (ok) {
+      const int64_t* ko = (const int64_t*)(b + h.off_koff);
+      const uint32_t* so = (const uint32_t*)(b + h.off_soff);
+      ok = ko[0] == 0 && ko[h.n] == h.nkeys;
+      for (int64_t i = 0; ok && i < h.n; ++i) {
+        const int64_t len = ko[i + 1] - ko[i];
+        const uint32_t* si = so + i * S1;
+        ok = len >= 0 && len <= 0x7fffffff && si[0] == 0 && (int64_t)si[h.S] == len;
+        for (int64_t q = 0; ok && q < (int64_t)h.S; ++q) ok = si[q] <= si[q + 1];
+      }
+    }
+    if (!ok) {
+      munmap(base, (size_t)st.st_size);
+      PBH_REQUIRE(false, "pass file %s is damaged (sections or offsets are inconsistent)", path.c_str());
+    }
+  }
   map_base_ = base;
   map_size_ = (size_t)st.st_size;
   pko_ = (const int64_t*)(b + h.off_koff);

@@ -2,6 +2,7 @@
 // Python layer does — multi-threaded text load with key collection, batch dealing, concurrent packing from
 // several threads, archive and pass-file round trips, host table bulk ops, SSD spill / promote, key sort.
 // Built three times by benchmarks/sanitize_host.sh: -fsanitize=address,undefined, -fsanitize=thread, plain.
+#include <algorithm>
 #include <atomic>
 #include <cstdio>
 #include <cstdlib>
@@ -114,6 +115,53 @@ int main(int argc, char** argv) {
     OK(pbh_dataset_pack_batch(ds2, 1, 0, keys.data(), off.data(), dense.data(), 1));
   }
   CHECK(pbh_dataset_slots_shuffle(ds2, nullptr, 0, 1) != 0);          // refused on a pass file
+  // damaged archives and pass files: truncated at many lengths, bytes flipped — an error or a clean load, never a
+  // read outside the mapping
+  {
+    auto slurp = [](const std::string& p) {
+      std::vector<char> v;
+      FILE* f = fopen(p.c_str(), "rb");
+      if (!f) return v;
+      fseek(f, 0, SEEK_END);
+      long n = ftell(f);
+      fseek(f, 0, SEEK_SET);
+      v.resize((size_t)n);
+      if (n && fread(v.data(), 1, (size_t)n, f) != (size_t)n) v.clear();
+      fclose(f);
+      return v;
+    };
+    auto spit = [](const std::string& p, const char* d, size_t n) {
+      FILE* f = fopen(p.c_str(), "wb");
+      if (n) fwrite(d, 1, n, f);
+      fclose(f);
+    };
+    const std::vector<char> a0 = slurp(arc), p0 = slurp(arena);
+    CHECK(!a0.empty() && !p0.empty());
+    const std::string bad = dir + "/san.damaged";
+    void* dd = make_dataset(S);
+    OK(pbh_dataset_set_int(dd, "batch_size", 64));
+    for (int t = 0; t < 60; ++t) {
+      const std::vector<char>& src = (t & 1) ? p0 : a0;
+      std::vector<char> v = src;
+      if (t % 3 == 0) v.resize(rnd() % v.size());                                   // truncated
+      else for (int k = 0; k < 8; ++k) v[rnd() % std::min<size_t>(v.size(), 4096)] ^= (char)(1 + rnd() % 255);   // header / early bytes flipped
+      spit(bad, v.data(), v.size());
+      int rc = (t & 1) ? pbh_dataset_load_arena(dd, bad.c_str()) : pbh_dataset_load_archive(dd, bad.c_str());
+      if (rc == 0) {                              // a damaged file may still be self-consistent: it must then be usable
+        if (pbh_dataset_prepare_train(dd, 1, 0, 0, 0) == 0 && pbh_dataset_num_batches(dd, 0) > 0) {
+          int B = 0; int64_t nk = 0;
+          if (pbh_dataset_batch_shape(dd, 0, 0, &B, &nk) == 0 && nk >= 0 && nk < (1 << 26)) {
+            std::vector<uint64_t> keys((size_t)nk + 1);
+            std::vector<int32_t> off((size_t)B * (S + 1) + S * B + 2);
+            std::vector<float> dense((size_t)B * 4);
+            pbh_dataset_pack_batch(dd, 0, 0, keys.data(), off.data(), dense.data(), 0);
+          }
+        }
+      }
+      pbh_dataset_release_memory(dd);
+    }
+    OK(pbh_dataset_destroy(dd));
+  }
   OK(pbh_dataset_release_memory(ds2));
   OK(pbh_dataset_destroy(ds2));
   std::vector<uint64_t> uk((size_t)nuniq);
