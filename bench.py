@@ -74,16 +74,18 @@ def parse_args():
 
 
 def reference_arm(args):
-    # The reference is a PaddlePaddle fork whose sparse engine (libbox_ps.so) is a closed binary
-    # fetched from an internal host; /root/reference has neither setup.py nor pyproject.toml
-    # (pip: "Directory '/root/reference' is not installable") and its CMake build needs ~40
-    # network-fetched third-party projects.  See DESIGN.md "Reference arm".
-    if int(os.environ.get("RANK", "0")) != 0:      # under torchrun: one line, from rank 0
+    """``--impl reference``: the reference's own open sparse engine (HeterPS, compiled unmodified
+    from /root/reference against thin shims) + fp32 cuBLAS towers + NCCL allreduce, same config,
+    same metric, same JSON line.  pip cannot install the reference (no setup.py / pyproject.toml,
+    closed libbox_ps.so, network-fetched CMake deps): see DESIGN.md "Reference arm" and
+    baseline/README.md.  None of this repo's models, kernels or engine is on that path."""
+    if args.model != "deepfm":
+        if int(os.environ.get("RANK", "0")) == 0:
+            print(json.dumps({"impl": "reference", "unavailable": "the reference arm covers the headline DeepFM config"}))
         return 0
-    print(json.dumps({"impl": "reference",
-                      "unavailable": "reference is not pip-installable offline (no setup.py/pyproject.toml; "
-                                     "BoxPS core libbox_ps.so is a closed binary; CMake build needs network)"}))
-    return 0
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "baseline"))
+    import reference_arm as ra
+    return ra.run(args)
 
 
 class ClockSampler:
