@@ -44,6 +44,8 @@ def parse_args():
     p.add_argument("--keys-per-gpu", type=int, default=125_000_000)
     p.add_argument("--hidden", default="512,256,128")
     p.add_argument("--n-batches", type=int, default=8, help="distinct synthetic batches rotated through")
+    p.add_argument("--load-factor", type=float, default=0.75,
+                   help="hash-table load factor (reference default 0.75, heter_comm.h:338)")
     p.add_argument("--no-flush", action="store_true", help="do not flush L2 between timed steps")
     p.add_argument("--profile-stages", action="store_true")
     p.add_argument("--no-graph", action="store_true", help="do not capture the step in a CUDA graph")
@@ -206,7 +208,7 @@ def main():
     max_keys = B * S * args.max_bag
     hidden = tuple(int(x) for x in args.hidden.split(","))
     box = BoxWrapper.set_instance(embedx_dim=args.dim, rank=rank, world_size=world)
-    capacity = int(args.keys_per_gpu / 0.6) + 1024        # load factor 0.6 (< reference's 0.75)
+    capacity = int(args.keys_per_gpu / args.load_factor) + 1024
     box.initialize_gpu_and_load_model({"mf_create_thresholds": 10.0}, table_capacity=capacity,
                                       max_keys_per_batch=max_keys)
     t0 = time.time()
@@ -385,6 +387,13 @@ def main():
         for k in ("debug_skip_h2d", "debug_skip_d2h", "debug_skip_build"):
             setattr(feed, k, False)
 
+    # ------------------------------------------------ correctness self-check (outside every timed region)
+    from paddlebox_b200.utils.selfcheck import sparse_selfcheck
+    try:
+        selfcheck = sparse_selfcheck(box, args.keys_per_gpu * world, rank, world)
+    except Exception as e:  # noqa: BLE001  (reported, never hidden: "ok": false)
+        selfcheck = {"ok": False, "error": str(e)[:300]}
+
     # max over ranks
     t = torch.tensor([dev_ms, e2e_ms, e2e_nf_ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -407,6 +416,7 @@ def main():
                        "dense_features": args.dense, "emb_dim": args.dim, "bag_len": f"U[1,{args.max_bag}]",
                        "avg_keys_per_batch_per_gpu": int(sum(h[3] for h in host_batches) / len(host_batches)),
                        "table_keys_per_gpu": args.keys_per_gpu, "table_keys_total": args.keys_per_gpu * world,
+                       "hash_load_factor": args.load_factor,
                        "mlp": [model.input_width, *hidden, 1] if args.model != "mmoe" else "8 experts 1024-512, 2 gates, 2 towers 256-128-1", "sparse_optimizer": "adagrad",
                        "dense_optimizer": "adam", "table_dtype": "fp32", "tower_dtype": "bf16 (fp32 accumulate)",
                        "l2": "flushed between timed steps (256 MB write)" if not args.no_flush else
@@ -423,6 +433,7 @@ def main():
             "gpu_launches": int(launches),
             "clocks": clocks,
             "loss": loss_val,
+            "selfcheck": selfcheck,
             "sparse_phases_us_rank0": sparse_phases,
             "wall_s_timed_region": round(wall, 3),
         }

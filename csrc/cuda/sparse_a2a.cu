@@ -119,7 +119,7 @@ k_sparse_pull(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPullArgsN args)
   const int lb = blockIdx.x % bpr;
   const PbxSparseDev& c = ctxs[vr];
   PbxPullArgs a = args.a[vr];
-  if (a.n_dev) a.n = (int64_t)__ldg(a.n_dev);
+  if (a.n_dev) a.n = max((int64_t)0, min((int64_t)__ldg(a.n_dev), a.n));   // never beyond the host-validated bound
   const int R = c.nranks;
   const uint32_t cap = c.cap;
   const int tid = threadIdx.x;
@@ -169,11 +169,14 @@ k_sparse_pull(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPullArgsN args)
       __syncthreads();
       if (is_rep) {
         uint32_t slot = s_base[owner] + lrank;
-        if (slot < cap) {
+        if (slot < cap - 1) {
           c.dd_uid[pos] = (uint32_t)owner * cap + slot;
           c.mail_keys[owner][(uint64_t)c.rank * cap + slot] = key;  // remote store (NVLink)
         } else {
-          c.dd_uid[pos] = (uint32_t)owner * cap;  // keep indices in range; flagged below
+          // Mailbox overflow: the key goes to the reserved LAST row of this owner's region, which is
+          // never shipped — its pulled values stay zero and its merged gradient is dropped — so no
+          // other key's values or table row are touched.  status 1 makes the next step fail loudly.
+          c.dd_uid[pos] = (uint32_t)owner * cap + (cap - 1);
           atomicExch(c.status, 1);
         }
       }
@@ -189,7 +192,7 @@ k_sparse_pull(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPullArgsN args)
     for (int64_t i = (int64_t)lb * PBX_A2A_THREADS + tid; i < a.n; i += stride)
       a.restore[i] = c.dd_uid[a.restore[i]];
     if (lb == 0 && tid < R) {
-      uint32_t n_send = min(c.send_cnt[tid], cap);
+      uint32_t n_send = min(c.send_cnt[tid], cap - 1);   // row cap-1 is the overflow row (see P1)
       c.send_cnt[tid] = n_send;
       c.mail_cnt[tid][c.rank] = n_send;  // remote store
     }
@@ -621,6 +624,7 @@ struct PbxSparseCtx {
   void* peer_base[PBX_MAX_RANKS];
   bool peer_opened[PBX_MAX_RANKS];
   int64_t max_keys;
+  int* status_host;        // pinned mirror of h.status, refreshed by a 4-byte copy after every push
   int grid_blocks;         // cooperative grid size (per real rank)
   void* table;             // PbxTable*
 };
@@ -656,8 +660,10 @@ int pbx_sparse_create(void** out, void* table, int rank, int nranks, int64_t max
   cudaGetDevice(&c->device);
   c->table = table;
   c->max_keys = max_keys;
-  if (cap <= 0) cap = nranks == 1 ? max_keys : (2 * max_keys / nranks + 1024);
-  if (cap > max_keys) cap = max_keys;
+  // (+1: the last row of every owner region is the overflow row, see k_sparse_pull P1)
+  if (cap <= 0) cap = nranks == 1 ? max_keys + 1 : (2 * max_keys / nranks + 1024);
+  if (cap > max_keys + 1) cap = max_keys + 1;
+  if (cap < 2) cap = 2;
   PBX_REQUIRE((uint64_t)cap * nranks < 0xFFFFFFF0ull, "mailbox too large");
   PbxSparseDev& h = c->h;
   h.rank = rank;
@@ -691,6 +697,8 @@ int pbx_sparse_create(void** out, void* table, int rank, int nranks, int64_t max
   PBX_CUDA_CHECK(cudaMalloc(&h.epoch, 256));
   PBX_CUDA_CHECK(cudaMemset(h.epoch, 0, 256));
   h.status = (int*)(h.epoch + 8);
+  PBX_CUDA_CHECK(cudaMallocHost(&c->status_host, 64));
+  memset(c->status_host, 0, 64);
   PBX_CUDA_CHECK(cudaMalloc(&c->d, sizeof(PbxSparseDev)));
   pbx_ctx_bind_peer(c, rank, c->symm_base);
   // cooperative grid: one CTA per SM
@@ -736,6 +744,7 @@ int pbx_sparse_destroy(void* hnd) {
   cudaFree(c->h.push_acc);
   cudaFree(c->h.epoch);
   cudaFree(c->d);
+  cudaFreeHost(c->status_host);
   delete c;
   return 0;
 }
@@ -814,11 +823,21 @@ int pbx_sparse_phase_times(void* hnd, uint64_t* out16, cudaStream_t st) {
   return 0;
 }
 
+// Non-blocking health check: the status word as of the last push whose 4-byte copy has completed
+// (every push enqueues one into pinned memory).  0 = healthy; see pbx_sparse_status for the codes.
+int pbx_sparse_status_peek(void* hnd) {
+  PbxSparseCtx* c = (PbxSparseCtx*)hnd;
+  return *(volatile int*)c->status_host;
+}
+
 int pbx_sparse_status(void* hnd, int* status, int reset, cudaStream_t st) {
   PbxSparseCtx* c = (PbxSparseCtx*)hnd;
   PBX_CUDA_CHECK(cudaMemcpyAsync(status, c->h.status, sizeof(int), cudaMemcpyDeviceToHost, st));
   PBX_CUDA_CHECK(cudaStreamSynchronize(st));
-  if (reset && *status) PBX_CUDA_CHECK(cudaMemsetAsync(c->h.status, 0, sizeof(int), st));
+  if (reset && *status) {
+    PBX_CUDA_CHECK(cudaMemsetAsync(c->h.status, 0, sizeof(int), st));
+    *c->status_host = 0;
+  }
   return 0;
 }
 
@@ -931,6 +950,8 @@ int pbx_sparse_push_dense(void* hnd, const uint32_t* d_restore, int64_t n, const
   PBX_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_sparse_push<false>, dim3(c->grid_blocks),
                                              dim3(PBX_PUSH_THREADS), kargs, pbx_push_smem(c->h), st));
   pbx_note_launch(1);
+  // status mirror for pbx_sparse_status_peek (a memcpy node when the step is captured in a graph)
+  PBX_CUDA_CHECK(cudaMemcpyAsync(c->status_host, c->h.status, sizeof(int), cudaMemcpyDeviceToHost, st));
   return 0;
 }
 

@@ -144,6 +144,27 @@ __global__ void k_lookup(PbxTableView t, const uint64_t* __restrict__ keys, int6
   }
 }
 
+// full value rows by key, one warp per key (coalesced row copy); absent keys give a zero row
+__global__ void k_fetch_rows(PbxTableView t, const uint64_t* __restrict__ keys, int64_t n, float* __restrict__ out,
+                             uint8_t* __restrict__ found) {
+  const int S = t.L.stride;
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t i = warp; i < n; i += nwarps) {
+    uint32_t s = PBX_NO_ROW;
+    if (lane == 0) {
+      const uint64_t key = keys[i];
+      s = (key == 0 || key == PBX_EMPTY_KEY) ? PBX_NO_ROW : pbx_dev_find(t, key);
+      if (found) found[i] = s != PBX_NO_ROW;
+    }
+    s = __shfl_sync(0xffffffffu, s, 0);
+    const float* row = t.vals + (uint64_t)s * S;
+    float* o = out + i * S;
+    for (int j = lane; j < S; j += 32) o[j] = (s == PBX_NO_ROW || j == S - 1) ? 0.f : row[j];
+  }
+}
+
 // unique keys only (caller merges duplicates first)
 __global__ void k_update(PbxTableView t, const uint64_t* __restrict__ keys, const float* __restrict__ push,
                          int push_stride, int64_t n) {
@@ -334,6 +355,18 @@ int pbx_table_lookup(void* h, const uint64_t* d_keys, int64_t n, float* d_out, i
   PBX_REQUIRE(out_stride >= 3 + t->view.L.embedx_dim, "lookup out_stride %d < hidden %d", out_stride,
               3 + t->view.L.embedx_dim);
   k_lookup<<<pbx_grid_for(n, 256), 256, 0, st>>>(t->view, d_keys, n, d_out, out_stride, d_rows_out);
+  PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
+  return 0;
+}
+
+// Full value rows [n, stride] of the given keys (zero rows, found = 0, for absent keys): the
+// by-key counterpart of pbx_table_dump — EndPass write-back of a pass's key list in bounded chunks
+// (reference dump_to_cpu, hashtable_kernel.cu:247-301), and the oracle side of bench.py's self-check.
+int pbx_table_fetch_rows(void* h, const uint64_t* d_keys, int64_t n, float* d_rows_out, uint8_t* d_found,
+                         cudaStream_t st) {
+  PbxTable* t = (PbxTable*)h;
+  if (n <= 0) return 0;
+  k_fetch_rows<<<pbx_grid_for(n * 32, 256), 256, 0, st>>>(t->view, d_keys, n, d_rows_out, d_found);
   PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);
   return 0;
 }

@@ -935,6 +935,24 @@ int Dataset::load_arena(const std::string& path) {
   return 0;
 }
 
+// multi-node equalisation: every rank must step the same number of times; the caller passes
+// allreduce(max) of the local count and the largest batches are split until the count is reached
+// (data_set.cc:2708-2750)
+static void equalise_batches(std::vector<std::vector<BatchRange>>* worker_batches, int64_t min_batches) {
+  if (min_batches <= 0) return;
+  for (auto& wb : *worker_batches) {
+    while ((int64_t)wb.size() < min_batches && !wb.empty()) {
+      size_t big = 0;
+      for (size_t i = 1; i < wb.size(); ++i) if (wb[i].len > wb[big].len) big = i;
+      if (wb[big].len < 2) break;
+      BatchRange a = wb[big];
+      int h = a.len / 2;
+      wb[big] = {a.start, h};
+      wb.push_back({a.start + h, a.len - h});
+    }
+  }
+}
+
 int Dataset::prepare_train(int nworkers, bool shuffle, uint64_t seed, int64_t min_batches) {
   PBH_REQUIRE(nworkers >= 1, "nworkers must be >= 1");
   if (arena_only_) {
@@ -957,6 +975,7 @@ int Dataset::prepare_train(int nworkers, bool shuffle, uint64_t seed, int64_t mi
       all.swap(mixed);
     }
     for (size_t i = 0; i < all.size(); ++i) worker_batches_[i % nworkers].push_back(all[i]);
+    equalise_batches(&worker_batches_, min_batches);
     return 0;
   }
   if (enable_pv_merge) {
@@ -973,21 +992,7 @@ int Dataset::prepare_train(int nworkers, bool shuffle, uint64_t seed, int64_t mi
   std::vector<BatchRange> all;
   compute_batch_ranges(n, batch_size, nworkers, &all);
   for (size_t i = 0; i < all.size(); ++i) worker_batches_[i % nworkers].push_back(all[i]);
-  // multi-node equalisation: every rank must step the same number of times; the caller passes
-  // allreduce(max) of the local count and surplus batches are split (data_set.cc:2708-2750)
-  if (min_batches > 0) {
-    for (auto& wb : worker_batches_) {
-      while ((int64_t)wb.size() < min_batches && !wb.empty()) {
-        size_t big = 0;
-        for (size_t i = 1; i < wb.size(); ++i) if (wb[i].len > wb[big].len) big = i;
-        if (wb[big].len < 2) break;
-        BatchRange a = wb[big];
-        int h = a.len / 2;
-        wb[big] = {a.start, h};
-        wb.push_back({a.start + h, a.len - h});
-      }
-    }
-  }
+  equalise_batches(&worker_batches_, min_batches);
   build_arena();
   return 0;
 }

@@ -40,6 +40,11 @@ int pbx_table_lookup(void* table, const uint64_t* d_keys, int64_t n, float* d_ou
                      uint32_t* d_rows_out, pbx_stream_t stream);
 int pbx_table_update(void* table, const uint64_t* d_keys, const float* d_push, int push_stride, int64_t n,
                      pbx_stream_t stream);
+/* full value rows [n, stride] by key (zero row + found = 0 when absent); d_found may be NULL.
+ * reference: dump_to_cpu (heter_ps/hashtable_kernel.cu:247-301) walks the whole table; this is the
+ * by-key form used for chunked EndPass write-back. */
+int pbx_table_fetch_rows(void* table, const uint64_t* d_keys, int64_t n, float* d_rows_out, uint8_t* d_found,
+                         pbx_stream_t stream);
 int pbx_table_shrink(void* table, float decay, float delete_threshold, float delete_after_unseen_days,
                      int64_t* kept, pbx_stream_t stream);
 
@@ -55,6 +60,10 @@ int pbx_sparse_connect_local(void* ctx, void* const* peers);
 int pbx_sparse_geometry(void* ctx, int64_t* cap, int64_t* n_unique_rows, int* pull_stride, int* push_stride);
 float* pbx_sparse_pull_values(void* ctx);
 int pbx_sparse_status(void* ctx, int* status, int reset, pbx_stream_t stream);
+/* Non-blocking: the status as of the last push whose 4-byte status copy has reached pinned host
+ * memory (every push enqueues one).  Lets the trainer fail at the NEXT step after a mailbox
+ * overflow / barrier timeout without synchronising. */
+int pbx_sparse_status_peek(void* ctx);
 /* Copies the 16 phase-boundary globaltimer stamps (ns) of the last pull (0..5) and push (8..12); synchronises. */
 int pbx_sparse_phase_times(void* ctx, uint64_t* out16, pbx_stream_t stream);
 int pbx_sparse_pull(void* ctx, const uint64_t* d_keys, int64_t n, uint32_t* d_restore, pbx_stream_t stream);

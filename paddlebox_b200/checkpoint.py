@@ -123,29 +123,73 @@ def named_persistables(model) -> list:
     return [(n, p) for n, p in model.named_parameters()] + [(n, b) for n, b in model.named_buffers()]
 
 
+def _is_fc_weight(name: str, t: torch.Tensor) -> bool:
+    """FC weights live as [out, in] here (the layout the tcgen05 towers read) and as [in, out] in a
+    reference checkpoint (``mul``/``fc`` ops compute X @ W): ``*.w_0`` tensors, and their Adam
+    moments, are written and read transposed in the last two dimensions."""
+    base = name
+    for suf in ("_moment1_0", "_moment2_0"):
+        if base.endswith(suf):
+            base = base[:-len(suf)]
+    return base.endswith(".w_0") and t.dim() >= 2
+
+
+def _to_file_layout(name: str, t: torch.Tensor) -> torch.Tensor:
+    return t.transpose(-1, -2).contiguous() if _is_fc_weight(name, t) else t
+
+
+def _from_file_layout(name: str, src: torch.Tensor, like: torch.Tensor) -> torch.Tensor:
+    """``src`` as read from the file -> the layout of ``like``; a shape that does not fit raises
+    (no silent reshape of a tensor that merely has the right number of elements)."""
+    want = tuple(like.shape)
+    if _is_fc_weight(name, like):
+        want_file = want[:-2] + (want[-1], want[-2])
+        if tuple(src.shape) != want_file:
+            raise ValueError(f"{name}: checkpoint holds shape {tuple(src.shape)}, expected {want_file} ([in, out])")
+        return src.transpose(-1, -2)
+    if tuple(src.shape) != want:
+        if src.numel() == like.numel() and (src.dim() <= 1 or like.dim() <= 1):
+            return src.reshape(want)             # [n] <-> [n, 1] / [1, n] vectors
+        raise ValueError(f"{name}: checkpoint holds shape {tuple(src.shape)}, expected {want}")
+    return src
+
+
+def _moment_items(items, optimizer_store):
+    """(name, view of m, view of v) per trainable parameter; the store lays parameters out in
+    ``module.parameters()`` order, which is NOT the order of ``named_dense_params`` — match by identity."""
+    off_of = {id(p): o for p, o in zip(optimizer_store.params, optimizer_store.offsets)}
+    out = []
+    for name, p in items:
+        if not getattr(p, "requires_grad", False) or id(p) not in off_of:
+            continue
+        off, n = off_of[id(p)], p.numel()
+        out.append((name, p, optimizer_store.m[off:off + n].view(p.shape), optimizer_store.v[off:off + n].view(p.shape)))
+    return out
+
+
 def save_persistables(model, dirname: str, optimizer_store=None, filename: str | None = None) -> list:
     """One file per variable (or one combined file when ``filename`` is given — the reference's
-    ``save_combine`` layout: the serialized tensors back to back in name order)."""
+    ``save_combine`` layout: the serialized tensors back to back in name order).  FC weights are
+    written in the reference's [in, out] layout (see ``_is_fc_weight``)."""
     os.makedirs(dirname, exist_ok=True)
     items = named_persistables(model)
     if optimizer_store is not None and getattr(optimizer_store, "m", None) is not None:
         # Adam moments with the reference's naming: <param>_moment1_0 / _moment2_0
-        for (name, p), off in zip([(n, q) for n, q in items if q.requires_grad], optimizer_store.offsets):
-            n = p.numel()
-            items.append((f"{name}_moment1_0", optimizer_store.m[off:off + n].view_as(p)))
-            items.append((f"{name}_moment2_0", optimizer_store.v[off:off + n].view_as(p)))
+        for name, p, m, v in _moment_items(list(items), optimizer_store):
+            items.append((f"{name}_moment1_0", m))
+            items.append((f"{name}_moment2_0", v))
     names = []
     if filename:
         with open(os.path.join(dirname, filename), "wb") as f:
             for name, t in sorted(items, key=lambda kv: kv[0]):
-                f.write(serialize_lod_tensor(t))
+                f.write(serialize_lod_tensor(_to_file_layout(name, t.detach())))
                 names.append(name)
         with open(os.path.join(dirname, filename + ".names"), "w") as f:
             f.write("\n".join(names))
         return names
     for name, t in items:
         with open(os.path.join(dirname, name), "wb") as f:
-            f.write(serialize_lod_tensor(t))
+            f.write(serialize_lod_tensor(_to_file_layout(name, t.detach())))
         names.append(name)
     return names
 
@@ -161,16 +205,15 @@ def load_persistables(model, dirname: str, optimizer_store=None, strict: bool = 
                     raise FileNotFoundError(path)
                 continue
             src, _ = deserialize_lod_tensor(open(path, "rb").read())
-            t.copy_(src.to(t.dtype).reshape(t.shape))
+            t.copy_(_from_file_layout(name, src.to(t.dtype), t))
             loaded.append(name)
         if optimizer_store is not None and getattr(optimizer_store, "m", None) is not None:
-            for (name, p), off in zip([(n, q) for n, q in items if q.requires_grad], optimizer_store.offsets):
-                n = p.numel()
-                for suffix, buf in (("_moment1_0", optimizer_store.m), ("_moment2_0", optimizer_store.v)):
+            for name, p, m, v in _moment_items(items, optimizer_store):
+                for suffix, buf in (("_moment1_0", m), ("_moment2_0", v)):
                     path = os.path.join(dirname, name + suffix)
                     if os.path.exists(path):
                         src, _ = deserialize_lod_tensor(open(path, "rb").read())
-                        buf[off:off + n].copy_(src.reshape(-1))
+                        buf.copy_(_from_file_layout(name + suffix, src.to(buf.dtype), buf))
                         loaded.append(name + suffix)
     fn = getattr(model, "mark_weights_dirty", None)
     if fn:

@@ -75,6 +75,7 @@ class DatasetBase:
         # FLAGS_padbox_dataset_merge_thread_num (default 20 in the reference): capped by the cores there are
         self._native.set("merge_thread_num", max(1, min(FLAGS.padbox_dataset_merge_thread_num, os.cpu_count() or 1, 8)))
         self._prepared_workers = 0
+        self._rank, self._world = 0, 1
         self._device = torch.device("cuda", torch.cuda.current_device()) if torch.cuda.is_available() \
             else torch.device("cpu")
 
@@ -360,6 +361,7 @@ class InMemoryDataset(DatasetBase):
         """Files are dealt round-robin over nodes (SetFileList, data_set.cc:1963-1975)."""
         self._native.set("rank", rank)
         self._native.set("world", world)
+        self._rank, self._world = int(rank), int(world)
 
     # pass data ---------------------------------------------------------------------------------
     def _bind_reader_cores(self, overlapped: bool):

@@ -26,6 +26,10 @@ from ..ops.seqpool import SeqpoolAttrs
 
 class CTRModelBase(nn.Module):
     n_labels = 1
+    # every dense op of these models consumes the pooled embeddings, so the push (= backward of the
+    # pull, the first op) runs after all dense gradients are final: the trainer may fold the dense
+    # allreduce into the push kernel.  A subclass that adds a dense-only branch must set this False.
+    dense_grads_final_before_push = True
 
     def __init__(self, num_slots: int, embedx_dim: int, dense_dim: int, use_data_norm: bool = False,
                  seqpool_attrs: SeqpoolAttrs | None = None):

@@ -115,6 +115,17 @@ class SparseTable:
                                           None, N.stream_ptr()))
         return out
 
+    def fetch_rows(self, keys: torch.Tensor, out: torch.Tensor | None = None, with_found: bool = False):
+        """Full value rows [n, layout.stride] of ``keys`` (zero rows for absent keys)."""
+        keys = keys.contiguous()
+        n = keys.numel()
+        if out is None:
+            out = torch.empty(n, self.layout.stride, dtype=torch.float32, device=self.device)
+        found = torch.empty(max(n, 1), dtype=torch.uint8, device=self.device) if with_found else None
+        N.check(N.cuda().pbx_table_fetch_rows(self._h, N.ptr(keys), C.c_int64(n), N.ptr(out), N.ptr(found),
+                                              N.stream_ptr()), "pbx_table_fetch_rows")
+        return (out, found[:n].bool()) if with_found else out
+
     def update(self, keys: torch.Tensor, push: torch.Tensor) -> None:
         """Apply merged push records [n, >= 4 + D] for *unique* keys."""
         keys = keys.contiguous()

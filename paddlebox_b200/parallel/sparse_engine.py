@@ -88,6 +88,7 @@ class SparseEngine:
         kernel; ``keys`` may then be a fixed-capacity buffer — this is what lets one captured
         CUDA graph serve batches of different lengths."""
         n = keys.numel()
+        self.peek_status()
         self.pulls_this_step = getattr(self, "pulls_this_step", 0) + 1
         if restore is None:
             restore = torch.empty(max(n, 1), dtype=torch.int32, device=keys.device)
@@ -130,6 +131,14 @@ class SparseEngine:
         N.check(N.cuda().pbx_sparse_push(self._h, N.ptr(restore), C.c_int64(restore.numel()), None, None, None, 0,
                                          0, 0, cvm_offset, 0, N.ptr(grads), N.ptr(key2slot), grads.shape[1], 1,
                                          C.c_float(grad_scale), N.stream_ptr()), "pbx_sparse_push")
+
+    def peek_status(self) -> None:
+        """Non-blocking: raises if an EARLIER step (whose status copy has reached the host) overflowed
+        a mailbox or timed out at a barrier — a faulty step stops training within a step or two
+        instead of at the end of the pass.  Costs one read of pinned memory."""
+        st = N.cuda().pbx_sparse_status_peek(self._h)
+        if st:
+            raise RuntimeError(STATUS_MSG.get(st, f"sparse engine status {st}"))
 
     def check_status(self) -> None:
         """Synchronising health check; raises on mailbox overflow / barrier timeout."""

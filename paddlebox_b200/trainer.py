@@ -67,7 +67,11 @@ class CTRTrainer:
             for n, p in named:
                 if n in lrs and id(p) in offs:
                     self.sync.async_table.set_lr_range(offs[id(p)], offs[id(p)] + p.numel(), lrs[n])
-        if self.world > 1 and not self.cfg.is_test:
+        # The folded allreduce runs inside the sparse push kernel, i.e. when the pull op's backward
+        # runs: every dense gradient must be final by then.  That holds when the pull is the first
+        # op of the forward and nothing dense is computed beside it — a property of the MODEL, so the
+        # model has to declare it (CTRModelBase does); any other module keeps the separate allreduce.
+        if self.world > 1 and not self.cfg.is_test and getattr(model, "dense_grads_final_before_push", False):
             self.sync.fold_into(getattr(self.box, "engine", None))
         if self.world > 1:
             self.store.broadcast_params(0)
@@ -208,6 +212,9 @@ class CTRTrainer:
     def train_step(self, batch) -> torch.Tensor:
         """forward + backward (= sparse push) + dense sync/update.  Returns the loss tensor
         (device; reading it is the caller's sync point)."""
+        eng = getattr(self.box, "engine", None)
+        if eng is not None:
+            eng.peek_status()        # a mailbox overflow / barrier timeout of an earlier step is fatal here
         g = getattr(self, "_graph", None)
         if g is not None and not self.cfg.is_test and batch.batch_size == self._static.batch_size \
                 and batch.num_slots == self._static.num_slots:
@@ -256,14 +263,40 @@ class CTRTrainer:
             self.dumper.dump_batch(batch.ins_ids, outs)
 
     # ---- one pass ---------------------------------------------------------------------------
+    def _deal_batches(self, dataset) -> int:
+        """Deals the loaded records into batches and returns the worker index to iterate.
+
+        One process per GPU: ``set_rank_world`` already gave this process only its own share of the
+        files (data_set.cc:1963-1975), so ALL local records belong to this rank: they are dealt to a
+        single local worker, and the batch count is equalised across ranks with an allreduce(max)
+        (data_set.cc:2708-2750) so that every rank enters the in-kernel barriers of pull / push the
+        same number of times.  Several workers inside one process (``world`` readers over one
+        in-memory dataset) keep the round-robin deal."""
+        sharded = self.world > 1 and getattr(dataset, "_world", 1) == self.world
+        if not sharded:
+            if dataset._prepared_workers == 0:
+                dataset.prepare_train(self.world, self.rank)
+            return self.rank if dataset._prepared_workers > 1 else 0
+        from .parallel.cluster import OP_MAX, Cluster
+        dataset.prepare_train(1, 0)
+        local = dataset.num_batches(0)
+        most = int(Cluster.ins().allreduce(int(local), OP_MAX))
+        if most > local:
+            if local == 0:
+                raise RuntimeError(f"rank {self.rank} loaded no trainable batch while another rank has {most}: "
+                                   "every rank needs at least batch_size records (give it more files)")
+            dataset.prepare_train(1, 0, min_batches=most)
+            if dataset.num_batches(0) != most:
+                raise RuntimeError(f"rank {self.rank}: cannot split {local} batches into {most} (too few records)")
+        return 0
+
     def train_from_dataset(self, dataset, print_period: int = 0, fetch_handler=None) -> dict:
         """Train every batch the dataset dealt to this worker; returns pass statistics."""
-        if dataset._prepared_workers == 0:
-            dataset.prepare_train(self.world, self.rank)
+        worker = self._deal_batches(dataset)
         t0 = time.time()
         n_ins, losses = 0, []
         want_ids = self.dumper is not None and bool(self.cfg.dump_fields)
-        for i, batch in enumerate(dataset.batches(worker=self.rank, with_ins_id=want_ids)):
+        for i, batch in enumerate(dataset.batches(worker=worker, with_ins_id=want_ids)):
             loss = self.train_step(batch)
             n_ins += batch.batch_size
             if print_period and (i + 1) % print_period == 0:

@@ -484,3 +484,30 @@ def cpu_router_edge_cases(rank, world):
     # keys 0 (registered by both ranks' feed pass on its owner), 7, 9 exist; 12345 was not created by the push
     assert int(total) in (3, 4) and abs(float(s) - 5.0) < 1e-5, (int(total), float(s))
     return True
+
+
+def cpu_train_from_dataset_sharded(rank, world, data_dir):
+    """Every rank loads ITS files (set_rank_world) and must train ALL of them, in the same number of
+    steps as its peers although the files differ in size."""
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    from paddlebox_b200.dataset import DatasetFactory
+    from paddlebox_b200.models.ctr import CtrDnn
+    from paddlebox_b200.trainer import CTRTrainer, TrainerConfig
+    from tests.util_data import slot_vars
+    box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=rank, world_size=world)
+    box.initialize_gpu_and_load_model({})
+    ds = DatasetFactory().create_dataset("PadBoxSlotDataset")
+    ds.set_use_var(slot_vars(3, 2))
+    ds.set_batch_size(16)
+    ds.set_thread(1)
+    ds.set_filelist(sorted(os.path.join(data_dir, f) for f in os.listdir(data_dir)))
+    ds.set_rank_world(rank, world)
+    ds.set_date("20240101")
+    ds.load_into_memory()
+    loaded = ds.get_memory_data_size()
+    ds.begin_pass()
+    torch.manual_seed(0)
+    trainer = CTRTrainer(CtrDnn(num_slots=3, embedx_dim=4, dense_dim=2, hidden=(8,)), box, TrainerConfig())
+    stats = trainer.train_from_dataset(ds)
+    ds.end_pass(False)
+    return {"loaded": int(loaded), "instances": int(stats["instances"]), "steps": int(stats["steps"])}

@@ -55,6 +55,31 @@ def test_lod_tensor_format_roundtrip_and_layout(tmp_path):
         assert n1 == n2 and torch.equal(p1, p2)
     for p, off in zip(store.params, store.offsets):      # (padding words between tensors are not saved)
         assert torch.equal(store.m[off:off + p.numel()], store2.m[off:off + p.numel()])
+    # asymmetric multi-layer tower: parameter order of the store (w0, w1, .., b0, b1, ..) differs
+    # from the checkpoint's name order (w0, b0, w1, b1, ..); moments must follow their parameter, and FC
+    # weights are stored in the reference's [in, out] layout
+    m3 = CtrDnn(num_slots=2, embedx_dim=4, dense_dim=1, hidden=(16, 8))
+    s3 = DenseParamStore(m3)
+    s3.m.normal_(); s3.v.uniform_()
+    ckpt.save_persistables(m3, str(tmp_path / "d3"), s3)
+    w0 = dict(m3.named_dense_params())["fc_0.w_0"]
+    on_disk, _ = ckpt.deserialize_lod_tensor(open(tmp_path / "d3" / "fc_0.w_0", "rb").read())
+    assert tuple(on_disk.shape) == (w0.shape[1], w0.shape[0]) and torch.equal(on_disk, w0.detach().t())
+    m4 = CtrDnn(num_slots=2, embedx_dim=4, dense_dim=1, hidden=(16, 8))
+    s4 = DenseParamStore(m4)
+    ckpt.load_persistables(m4, str(tmp_path / "d3"), s4)
+    for (n1, p1), (n2, p2) in zip(m3.named_dense_params(), m4.named_dense_params()):
+        assert n1 == n2 and torch.equal(p1, p2)
+    off3 = {id(p): o for p, o in zip(s3.params, s3.offsets)}
+    off4 = {id(p): o for p, o in zip(s4.params, s4.offsets)}
+    for (n1, p1), (n2, p2) in zip(m3.named_dense_params(), m4.named_dense_params()):
+        a, b, n = off3[id(p1)], off4[id(p2)], p1.numel()
+        assert torch.equal(s3.m[a:a + n], s4.m[b:b + n]) and torch.equal(s3.v[a:a + n], s4.v[b:b + n]), n1
+    # a tensor of the right size but the wrong shape is refused, not reshaped
+    m5 = CtrDnn(num_slots=2, embedx_dim=4, dense_dim=1, hidden=(8, 16))
+    import pytest as _pt
+    with _pt.raises(ValueError):
+        ckpt.load_persistables(m5, str(tmp_path / "d3"), strict=False)
 
 
 def test_metric_variants():

@@ -267,6 +267,68 @@ def test_sparse_pull_push_virtual_ranks(nranks, dim, opt):
     assert n_multi > 0      # the test really exercised keys pushed by several requesters
 
 
+def test_sparse_mailbox_overflow_is_contained_and_reported():
+    """More unique keys for one shard than the mailbox holds: the surplus keys pull zeros and their
+    gradients are dropped; no other key's values or table row are affected; status reports it."""
+    from paddlebox_b200.parallel.sparse_engine import EmulatedSparseGroup
+    gen = torch.Generator().manual_seed(5)
+    nranks, dim, B, S = 2, 8, 48, 4
+    H = 3 + dim
+    tables = [_mk_table(cap=1 << 14, dim=dim) for _ in range(nranks)]
+    oracle = _mk_table(cap=1 << 16, dim=dim)
+    batches = [_bags(B, S, 5, 2000, gen) for _ in range(nranks)]
+    batches = [(k.to(dev()), l.to(dev())) for k, l in batches]
+    allk = torch.cat([k for k, _ in batches]).unique()
+    _prime(oracle, allk, dim)
+    ok, orow = oracle.dump()
+
+    def mix64(k):
+        m = (1 << 64) - 1
+        k ^= k >> 33
+        k = (k * 0xff51afd7ed558ccd) & m
+        k ^= k >> 33
+        k = (k * 0xc4ceb9fe1a85ec53) & m
+        k ^= k >> 33
+        return k
+    owner = torch.tensor([(mix64(int(k)) >> 40) % nranks for k in ok.tolist()], device=dev())
+    for r in range(nranks):
+        tables[r].insert(ok[owner == r], orow[owner == r])
+    before = [t.dump() for t in tables]
+    grp = EmulatedSparseGroup(tables, max_keys=max(k.numel() for k, _ in batches) + 8, cap=64)
+    restores = grp.pull([k for k, _ in batches])
+    with pytest.raises(RuntimeError, match="overflow"):
+        grp.check_status()
+    zero_keys = set()
+    for r, (k, _) in enumerate(batches):
+        got = grp.engines[r].values[restores[r].long()][:, :H]
+        exp = oracle.lookup(k)
+        same = (got == exp).all(1)
+        zero = (got == 0).all(1)
+        assert bool((same | zero).all()), "an overflowed key must pull zeros, every other key its own row"
+        assert bool(zero.any()) and bool(same.any())
+        zero_keys.update(k[zero & ~same].tolist())
+    douts = [torch.randn(B, S * H, device=dev()) for _ in range(nranks)]
+    cvms = [torch.stack([torch.ones(B, device=dev()), torch.zeros(B, device=dev())], 1) for _ in range(nranks)]
+    grp.push_pooled(restores, douts, cvms, [l for _, l in batches], B, S, H, 2, 0, -float(B))
+    with pytest.raises(RuntimeError, match="overflow"):
+        grp.check_status()
+    pushed_ok = set()
+    for r, (k, _) in enumerate(batches):
+        got = grp.engines[r].values[restores[r].long()][:, :H]
+        pushed_ok.update(k[~(got == 0).all(1)].tolist())
+    n_untouched = 0
+    for r in range(nranks):
+        ak, ar = tables[r].dump()
+        bmap = {int(kk): row for kk, row in zip(before[r][0].tolist(), before[r][1].cpu())}
+        for kk, row in zip(ak.tolist(), ar.cpu()):
+            if kk not in pushed_ok:           # overflowed on every requester (or never requested): row untouched
+                assert torch.equal(row, bmap[kk]), kk
+                n_untouched += 1
+            else:
+                assert float(row[0]) > float(bmap[kk][0])          # show count grew: the push arrived
+    assert n_untouched > 0
+
+
 # ------------------------------------------------------------------ seqpool
 @pytest.mark.parametrize("cfg", [
     dict(),

@@ -96,6 +96,24 @@ def test_one_rank_per_node_topology_gloo():
     assert all(_spawn(W.cpu_one_rank_per_node, 3, "gloo"))
 
 
+def test_train_from_dataset_trains_every_local_record_two_ranks(tmp_path):
+    """ADVICE r1 (high): with one process per GPU each rank loads files[rank::world]; the trainer must train
+    all of them (not 1/world of them) and all ranks must step equally often."""
+    from tests.util_data import write_files
+    d = tmp_path / "data"
+    d.mkdir()
+    write_files(str(d), n_files=1, lines_per_file=200, n_sparse=3, n_dense=2, key_space=30)       # rank 0's file
+    import os
+    os.rename(d / os.listdir(d)[0], d / "a_part")
+    write_files(str(d), n_files=1, lines_per_file=120, n_sparse=3, n_dense=2, key_space=30)       # rank 1's file
+    other = [f for f in os.listdir(d) if f != "a_part"][0]
+    os.rename(d / other, d / "b_part")
+    outs = _spawn(W.cpu_train_from_dataset_sharded, 2, "gloo", args=(str(d),))
+    assert outs[0]["loaded"] == 200 and outs[1]["loaded"] == 120
+    assert outs[0]["instances"] == 200 and outs[1]["instances"] == 120           # nothing dropped
+    assert outs[0]["steps"] == outs[1]["steps"] == 13                               # ceil(200 / 16), equalised
+
+
 def _ngpu():
     return torch.cuda.device_count() if torch.cuda.is_available() else 0
 
