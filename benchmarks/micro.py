@@ -228,6 +228,27 @@ def bench_sparse(out, flush, keys_per_gpu=125_000_000, dim=16, B=4096, S=26, max
           "push": {n: round((t[9 + i] - t[8 + i]) / 1e3, 1) for i, n in enumerate(names_push)}}
     out.append(ph)
     print(ph, flush=True)
+    # load balance across the CTAs of the persistent kernels: when did each CTA FINISH a phase's work
+    # (before waiting at the barrier that ends it)?  first / median / last finisher after the phase began
+    import numpy as np
+    grid = C.c_int()
+    N.check(N.cuda().pbx_sparse_debug_stamps(eng._h, 1, None, C.byref(grid), N.stream_ptr()))
+    flush.zero_()
+    pull()
+    flush.zero_()
+    push()
+    buf = (C.c_uint64 * (grid.value * 16))()
+    N.check(N.cuda().pbx_sparse_debug_stamps(eng._h, 1, buf, C.byref(grid), N.stream_ptr()))
+    N.check(N.cuda().pbx_sparse_phase_times(eng._h, ts, N.stream_ptr()))
+    t = [int(x) for x in ts]
+    st = np.frombuffer(buf, dtype=np.uint64).reshape(grid.value, 16).astype(np.int64)
+    imb = {"kernel": "phase_finish_us_over_ctas (first / median / last finisher, since the phase began)"}
+    for name, slot, begin in [("P0", 0, t[0]), ("P1", 1, t[1]), ("P2a", 2, t[2]), ("P2b", 3, t[3]), ("P3", 4, t[4]),
+                              ("Q0", 8, t[8]), ("Q1", 9, t[9]), ("Q2", 10, t[10]), ("Q3", 11, t[11])]:
+        d = (st[:, slot] - begin) / 1e3
+        imb[name] = [round(float(d.min()), 1), round(float(np.median(d)), 1), round(float(d.max()), 1)]
+    out.append(imb)
+    print(imb, flush=True)
 
 
 def main():

@@ -67,6 +67,9 @@ struct PbxPushArgsN { PbxPushArgs a[PBX_MAX_RANKS]; };
 
 // phase timestamps (one thread, globaltimer) for benchmarks/micro.py --phases; slots live after the epoch word
 #define PBX_TS(i) do { if (lb == 0 && tid == 0) c.epoch[16 + (i)] = pbx_globaltimer(); } while (0)
+// per-CTA stamp taken when the CTA FINISHES the work of a phase, before it waits for the others
+// (diagnosis of load imbalance; only when pbx_sparse_debug_stamps switched it on)
+#define PBX_TSB(i) do { if (c.dbg && tid == 0) c.dbg[(size_t)lb * 16 + (i)] = pbx_globaltimer(); } while (0)
 
 namespace {
 
@@ -129,60 +132,109 @@ k_sparse_pull(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPullArgsN args)
   __shared__ uint32_t s_cnt[PBX_MAX_RANKS];
   __shared__ uint32_t s_base[PBX_MAX_RANKS];
 
-  // ---- P0: reset per-batch counters (dedup table was cleaned by the previous pull)
-  if (lb == 0 && tid < R) c.send_cnt[tid] = 0;
+  // ---- P0: reset per-batch counters and (re)write the whole dedup table as EMPTY.  Writing it here
+  // rather than after its last use leaves its lines resident (dirty) in L2, so the hash-insert
+  // atomics of P1 are L2 hits instead of one random HBM access each; full-line writes fetch nothing.
+  if (lb == 0 && tid < R) {
+    c.send_cnt[tid] = 0;
+    c.send_cnt[32 + tid] = 0;     // P3 tile tickets
+  }
+  {
+    const int64_t stride = (int64_t)bpr * PBX_A2A_THREADS;
+    ulonglong2* dk = reinterpret_cast<ulonglong2*>(c.dd_keys);
+    const ulonglong2 e2 = make_ulonglong2(PBX_EMPTY_KEY, PBX_EMPTY_KEY);
+    for (int64_t i = (int64_t)lb * PBX_A2A_THREADS + tid; i < (int64_t)(c.dd_cap >> 1); i += stride) dk[i] = e2;
+  }
+  PBX_TSB(0);
   grid.sync();
   PBX_TS(1);
 
-  // ---- P1: dedup + claim a mailbox slot per unique key + ship the key to its owner
+  // ---- P1: dedup + claim a mailbox slot per unique key + ship the key to its owner.
+  // Every thread handles KPT keys per round with their first hash-table CAS all in flight at once
+  // (the CAS round trips to L2, not the arithmetic, are what this phase costs); a batch of up to
+  // bpr * 1024 * KPT occurrences is one round, i.e. one set of block barriers.
   {
+    constexpr int KPT = 3;
     const uint32_t mask = c.dd_cap - 1;
-    const int64_t chunk = (int64_t)bpr * PBX_A2A_THREADS;
+    const int64_t chunk = (int64_t)bpr * PBX_A2A_THREADS * KPT;
     const int64_t nround = (a.n + chunk - 1) / chunk;
     for (int64_t r = 0; r < nround; ++r) {
-      int64_t i = r * chunk + (int64_t)lb * PBX_A2A_THREADS + tid;
+      const int64_t base = r * chunk + (int64_t)lb * PBX_A2A_THREADS * KPT + tid;
       if (tid < R) s_cnt[tid] = 0;
       __syncthreads();
-      bool is_rep = false;
-      uint32_t pos = 0, lrank = 0;
-      int owner = 0;
-      uint64_t key = 0;
-      if (i < a.n) {
-        key = a.keys[i];
-        uint64_t h = pbx_mix64(key);
-        pos = (uint32_t)h & mask;
+      uint64_t key[KPT];
+      uint32_t pos[KPT], lrank[KPT];
+      int owner[KPT];
+      bool is_rep[KPT], done[KPT];
+#pragma unroll
+      for (int u = 0; u < KPT; ++u) {
+        const int64_t i = base + (int64_t)u * PBX_A2A_THREADS;
+        is_rep[u] = false;
+        done[u] = i >= a.n;
+        key[u] = done[u] ? 0 : a.keys[i];
+        pos[u] = (uint32_t)pbx_mix64(key[u]) & mask;
+      }
+      unsigned long long prev[KPT];
+#pragma unroll
+      for (int u = 0; u < KPT; ++u)      // first probe of every key: independent atomics, all in flight
+        if (!done[u])
+          prev[u] = atomicCAS(reinterpret_cast<unsigned long long*>(c.dd_keys + pos[u]),
+                              (unsigned long long)PBX_EMPTY_KEY, (unsigned long long)key[u]);
+#pragma unroll
+      for (int u = 0; u < KPT; ++u) {
+        if (done[u]) continue;
         while (true) {
-          unsigned long long prev = atomicCAS(reinterpret_cast<unsigned long long*>(c.dd_keys + pos),
-                                              (unsigned long long)PBX_EMPTY_KEY, (unsigned long long)key);
-          if (prev == PBX_EMPTY_KEY) { is_rep = true; break; }
-          if (prev == key) break;
-          pos = (pos + 1) & mask;
+          if (prev[u] == PBX_EMPTY_KEY) { is_rep[u] = true; break; }
+          if (prev[u] == key[u]) break;
+          pos[u] = (pos[u] + 1) & mask;
+          prev[u] = atomicCAS(reinterpret_cast<unsigned long long*>(c.dd_keys + pos[u]),
+                              (unsigned long long)PBX_EMPTY_KEY, (unsigned long long)key[u]);
         }
-        a.restore[i] = pos;
-        if (is_rep) {
-          owner = pbx_owner_of(key, R);
-          lrank = atomicAdd(&s_cnt[owner], 1u);
+        a.restore[base + (int64_t)u * PBX_A2A_THREADS] = pos[u];
+        c.occ_rep[base + (int64_t)u * PBX_A2A_THREADS] = is_rep[u] ? 1 : 0;
+      }
+#pragma unroll
+      for (int u = 0; u < KPT; ++u) owner[u] = is_rep[u] ? pbx_owner_of(key[u], R) : -1;
+      // rank of every representative among its CTA's keys for the same owner: one shared-memory
+      // atomic per (warp, owner) instead of one per key (with few ranks thousands of lanes would
+      // otherwise queue on the same shared word)
+      {
+        const unsigned lane = tid & 31;
+#pragma unroll
+        for (int u = 0; u < KPT; ++u) {
+          for (int o = 0; o < R; ++o) {
+            const unsigned m = __ballot_sync(0xffffffffu, owner[u] == o);
+            if (m == 0) continue;
+            const int leader = __ffs(m) - 1;
+            uint32_t b0 = 0;
+            if ((int)lane == leader) b0 = atomicAdd(&s_cnt[o], (uint32_t)__popc(m));
+            b0 = __shfl_sync(0xffffffffu, b0, leader);
+            if (owner[u] == o) lrank[u] = b0 + __popc(m & ((1u << lane) - 1u));
+          }
         }
       }
       __syncthreads();
       if (tid < R) s_base[tid] = s_cnt[tid] ? atomicAdd(c.send_cnt + tid, s_cnt[tid]) : 0u;
       __syncthreads();
-      if (is_rep) {
-        uint32_t slot = s_base[owner] + lrank;
+#pragma unroll
+      for (int u = 0; u < KPT; ++u) {
+        if (!is_rep[u]) continue;
+        const uint32_t slot = s_base[owner[u]] + lrank[u];
         if (slot < cap - 1) {
-          c.dd_uid[pos] = (uint32_t)owner * cap + slot;
-          c.mail_keys[owner][(uint64_t)c.rank * cap + slot] = key;  // remote store (NVLink)
+          c.dd_uid[pos[u]] = (uint32_t)owner[u] * cap + slot;
+          c.mail_keys[owner[u]][(uint64_t)c.rank * cap + slot] = key[u];  // remote store (NVLink)
         } else {
           // Mailbox overflow: the key goes to the reserved LAST row of this owner's region, which is
           // never shipped — its pulled values stay zero and its merged gradient is dropped — so no
           // other key's values or table row are touched.  status 1 makes the next step fail loudly.
-          c.dd_uid[pos] = (uint32_t)owner * cap + (cap - 1);
+          c.dd_uid[pos[u]] = (uint32_t)owner[u] * cap + (cap - 1);
           atomicExch(c.status, 1);
         }
       }
       __syncthreads();
     }
   }
+  PBX_TSB(1);
   grid.sync();
   PBX_TS(2);
 
@@ -197,13 +249,9 @@ k_sparse_pull(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPullArgsN args)
       c.mail_cnt[tid][c.rank] = n_send;  // remote store
     }
   }
-  grid.sync();  // all reads of dd_uid done before dd_keys is recycled
+  PBX_TSB(2);
   PBX_TS(3);
-  {
-    const int64_t stride = (int64_t)bpr * PBX_A2A_THREADS;
-    for (int64_t i = (int64_t)lb * PBX_A2A_THREADS + tid; i < (int64_t)c.dd_cap; i += stride)
-      c.dd_keys[i] = PBX_EMPTY_KEY;
-  }
+  PBX_TSB(3);
   xbarrier<EMU>(grid, c, e0 + 1, lb == 0);
   PBX_TS(4);
 
@@ -223,6 +271,10 @@ k_sparse_pull(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPullArgsN args)
     const int nper = nwarps >= R ? nwarps / R : nwarps;
     const int grp = nwarps >= R ? warp % R : 0;
     const int widx = nwarps >= R ? warp / R : warp;
+    // Tiles of 32 keys are handed out through one ticket counter per requester (send_cnt[32 + s],
+    // zeroed in P0): a warp that drew cheap tiles takes more of them, so the phase ends when the
+    // work does instead of when the unluckiest warp of a static split is done.  The next ticket is
+    // drawn before the current tile is processed (its round trip hides behind the tile).
     for (int sr = 0; sr < (nwarps >= R ? 1 : R); ++sr) {
       if (nwarps >= R && widx >= nper) break;
       const int s = (c.rank + 1 + grp + sr) % R;
@@ -230,7 +282,14 @@ k_sparse_pull(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPullArgsN args)
       const uint64_t* mk = c.mail_keys[c.rank] + (uint64_t)s * cap;
       uint32_t* mrow = c.mail_row + (uint64_t)s * cap;
       float* dst = c.pull_vals[s] + (uint64_t)c.rank * cap * PS;  // requester s, my region
-      for (uint32_t j0 = (uint32_t)widx * 32u; j0 < cnt; j0 += (uint32_t)nper * 32u) {
+      uint32_t* ticket = c.send_cnt + 32 + s;
+      uint32_t tk = 0;
+      if (lane == 0) tk = atomicAdd(ticket, 1u);
+      tk = __shfl_sync(0xffffffffu, tk, 0);
+      while ((uint64_t)tk * 32u < cnt) {
+        const uint32_t j0 = tk * 32u;
+        uint32_t tk_next = 0;
+        if (lane == 0) tk_next = atomicAdd(ticket, 1u);
         uint32_t j = j0 + lane;
         uint32_t row = PBX_NO_ROW;
         if (j < cnt) {
@@ -240,21 +299,36 @@ k_sparse_pull(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPullArgsN args)
         }
         const uint32_t nvalid = min(32u, cnt - j0);
         const uint32_t items = nvalid * (uint32_t)chunks;
-        for (uint32_t it0 = 0; it0 < items; it0 += 32) {
-          uint32_t it = it0 + lane;
-          uint32_t kk = min(it / (uint32_t)chunks, 31u);
-          uint32_t ch = it % (uint32_t)chunks;
-          uint32_t r = __shfl_sync(0xffffffffu, row, kk);
-          if (it < items) {
-            float4 v = zero4;
-            if (r != PBX_NO_ROW)
-              v = *reinterpret_cast<const float4*>(c.table.vals + (uint64_t)r * c.table.L.stride + ch * 4);
-            *reinterpret_cast<float4*>(dst + (uint64_t)(j0 + kk) * PS + ch * 4) = v;  // remote store
+        // UN independent 16-byte row loads per lane are issued before the first remote store needs
+        // its data (a store right behind its load would hold the warp for a full HBM round trip per
+        // chunk: 128 lines in flight per SM instead of the several hundred the memory system takes)
+        constexpr int UN = 5;
+        for (uint32_t it0 = 0; it0 < items; it0 += 32 * UN) {
+          float4 v[UN];
+#pragma unroll
+          for (int u = 0; u < UN; ++u) {
+            const uint32_t it = it0 + u * 32 + lane;
+            const uint32_t kk = min(it / (uint32_t)chunks, 31u);
+            const uint32_t ch = it % (uint32_t)chunks;
+            const uint32_t r = __shfl_sync(0xffffffffu, row, kk);
+            v[u] = zero4;
+            if (it < items && r != PBX_NO_ROW)
+              v[u] = __ldcg(reinterpret_cast<const float4*>(c.table.vals + (uint64_t)r * c.table.L.stride + ch * 4));
+          }
+#pragma unroll
+          for (int u = 0; u < UN; ++u) {
+            const uint32_t it = it0 + u * 32 + lane;
+            if (it < items) {
+              const uint32_t kk = it / (uint32_t)chunks, ch = it % (uint32_t)chunks;
+              *reinterpret_cast<float4*>(dst + (uint64_t)(j0 + kk) * PS + ch * 4) = v[u];  // remote store
+            }
           }
         }
+        tk = __shfl_sync(0xffffffffu, tk_next, 0);
       }
     }
   }
+  PBX_TSB(4);
   xbarrier<EMU>(grid, c, e0 + 2, lb == 0);
   PBX_TS(5);
   if (lb == 0 && tid == 0) *c.epoch = e0 + 2;
@@ -279,19 +353,10 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
   const uint64_t e0 = *c.epoch;
   PBX_TS(8);
 
-  // ---- Q0: zero the merge rows in use
-  for (int o = 0; o < R; ++o) {
-    const int64_t items = (int64_t)c.send_cnt[o] * pchunks;
-    float4* base = reinterpret_cast<float4*>(c.push_acc + (uint64_t)o * cap * PD);
-    for (int64_t it = gtid; it < items; it += gstride) base[it] = make_float4(0.f, 0.f, 0.f, 0.f);
-  }
-  grid.sync();
-  PBX_TS(9);
-
-  // ---- Q1: merge by unique key (fused with the seqpool/CVM backward in mode 0)
+  // ---- Q0: initialise the merge rows in use.  Fast path (pooled gradients, cvm_offset 2): the
+  // representative occurrence of every unique key STORES its record (no zero pass, no atomics);
+  // other paths zero the rows and merge everything with atomics in Q1.
   if (a.mode == 0 && a.cvm_offset == 2) {
-    // one thread per (bag, 4-word chunk of the push record); chunks beyond the first are added
-    // with a single 16-byte vector reduction per occurrence
     const int hidden = 3 + c.table.L.embedx_dim;
     const int64_t items = (int64_t)a.S * a.B * pchunks;
     for (int64_t it = gtid; it < items; it += gstride) {
@@ -301,6 +366,50 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
       const int b = (int)(g % a.B);
       const int32_t k0 = __ldg(a.lod + g), k1 = __ldg(a.lod + g + 1);
       if (k0 >= k1) continue;
+      float4 v;
+      float* vp = reinterpret_cast<float*>(&v);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int col = ch * 4 + j - 1;  // push word w <-> value column w - 1
+        if (col < 0) vp[j] = (float)s;   // word 0 = slot id
+        else if (col >= hidden) vp[j] = 0.f;
+        else if (col < 2) vp[j] = __ldg(a.cvm + (int64_t)b * 2 + col);
+        else vp[j] = a.grad_scale * __ldg(a.dout + (int64_t)b * a.ld_dout + (int64_t)s * a.Eo + (col - a.dim_off));
+      }
+      for (int32_t k = k0; k < k1; ++k)
+        if (c.occ_rep[k])
+          *reinterpret_cast<float4*>(c.push_acc + (uint64_t)__ldg(a.restore + k) * PD + ch * 4) = v;
+    }
+  } else {
+    for (int o = 0; o < R; ++o) {
+      const int64_t items = (int64_t)c.send_cnt[o] * pchunks;
+      float4* base = reinterpret_cast<float4*>(c.push_acc + (uint64_t)o * cap * PD);
+      for (int64_t it = gtid; it < items; it += gstride) base[it] = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+  }
+  PBX_TSB(8);
+  grid.sync();
+  PBX_TS(9);
+
+  // ---- Q1: merge by unique key (fused with the seqpool/CVM backward in mode 0)
+  if (a.mode == 0 && a.cvm_offset == 2) {
+    // One thread per (bag, 4-word chunk of the push record).  In CTR batches almost every unique
+    // key occurs once, so the merge is done in two passes instead of with one atomic per word:
+    //   pass A (before the grid barrier above... see Q0): every REPRESENTATIVE occurrence (the
+    //          first claimer of its key in the pull's dedup, c.occ_rep) STORES its record;
+    //   pass B (here): the few remaining occurrences are added with atomics / vector reductions.
+    // (reference: PushMergeCopy vs PushMergeCopyAtomic chosen by total < 2 * uniq, box_wrapper.cu:1034)
+    const int hidden = 3 + c.table.L.embedx_dim;
+    const int64_t items = (int64_t)a.S * a.B * pchunks;
+    for (int64_t it = gtid; it < items; it += gstride) {
+      const int ch = (int)(it % pchunks);
+      const int64_t g = it / pchunks;
+      const int s = (int)(g / a.B);
+      const int b = (int)(g % a.B);
+      const int32_t k0 = __ldg(a.lod + g), k1 = __ldg(a.lod + g + 1);
+      bool any = false;
+      for (int32_t k = k0; k < k1; ++k) any |= (c.occ_rep[k] == 0);
+      if (!any) continue;
       float v[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
@@ -310,9 +419,9 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
         else v[j] = a.grad_scale * __ldg(a.dout + (int64_t)b * a.ld_dout + (int64_t)s * a.Eo + (col - a.dim_off));
       }
       for (int32_t k = k0; k < k1; ++k) {
+        if (c.occ_rep[k]) continue;
         float* rec = c.push_acc + (uint64_t)__ldg(a.restore + k) * PD + ch * 4;
         if (ch == 0) {
-          rec[0] = (float)s;
           atomicAdd(rec + 1, v[1]);
           atomicAdd(rec + 2, v[2]);
           atomicAdd(rec + 3, v[3]);
@@ -353,6 +462,7 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
       if (col == 0) rec[0] = (float)a.key2slot[i];
     }
   }
+  PBX_TSB(9);
   grid.sync();
   PBX_TS(10);
 
@@ -383,6 +493,7 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
       }
     }
   }
+  PBX_TSB(10);
   xbarrier<EMU>(grid, c, e0 + 1, lb == 0);
   PBX_TS(11);
 
@@ -599,6 +710,7 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
       if (s + 1 < R) grid.sync();
     }
   }
+  PBX_TSB(11);
   PBX_TS(12);
   if (a.dense_ctx) {
     xbarrier<EMU>(grid, c, e0 + 2, lb == 0);   // every peer's reduced slices have landed
@@ -694,6 +806,8 @@ int pbx_sparse_create(void** out, void* table, int rank, int nranks, int64_t max
   PBX_CUDA_CHECK(cudaMemset(h.serve_cnt, 0, 64 * sizeof(uint32_t)));
   PBX_CUDA_CHECK(cudaMalloc(&h.mail_row, (size_t)nranks * cap * sizeof(uint32_t)));
   PBX_CUDA_CHECK(cudaMalloc(&h.push_acc, (size_t)nranks * cap * h.push_stride * sizeof(float)));
+  PBX_CUDA_CHECK(cudaMalloc(&h.occ_rep, (size_t)max_keys + 16));
+  PBX_CUDA_CHECK(cudaMemset(h.occ_rep, 0, (size_t)max_keys + 16));
   PBX_CUDA_CHECK(cudaMalloc(&h.epoch, 256));
   PBX_CUDA_CHECK(cudaMemset(h.epoch, 0, 256));
   h.status = (int*)(h.epoch + 8);
@@ -742,6 +856,7 @@ int pbx_sparse_destroy(void* hnd) {
   cudaFree(c->h.serve_cnt);
   cudaFree(c->h.mail_row);
   cudaFree(c->h.push_acc);
+  cudaFree(c->h.occ_rep);
   cudaFree(c->h.epoch);
   cudaFree(c->d);
   cudaFreeHost(c->status_host);
@@ -811,6 +926,24 @@ static int pbx_ctx_sync_dev(PbxSparseCtx* c, cudaStream_t st) {
     PBX_CUDA_CHECK(cudaMemcpyAsync(c->d, &c->h, sizeof(PbxSparseDev), cudaMemcpyHostToDevice, st));
     PBX_CUDA_CHECK(cudaStreamSynchronize(st));  // h is pageable: make the copy complete before h changes
     c->dirty = false;
+  }
+  return 0;
+}
+
+// Diagnosis: per-CTA phase-end stamps.  on = 1 allocates [grid, 16] uint64 and switches the stamps on;
+// out (host, [grid * 16]) receives the stamps of the last pull (slots 0..4) and push (8..11).
+int pbx_sparse_debug_stamps(void* hnd, int on, uint64_t* out, int* grid_out, cudaStream_t st) {
+  PbxSparseCtx* c = (PbxSparseCtx*)hnd;
+  if (grid_out) *grid_out = c->grid_blocks;
+  if (on && !c->h.dbg) {
+    PBX_CUDA_CHECK(cudaMalloc(&c->h.dbg, (size_t)c->grid_blocks * 16 * sizeof(uint64_t)));
+    PBX_CUDA_CHECK(cudaMemset(c->h.dbg, 0, (size_t)c->grid_blocks * 16 * sizeof(uint64_t)));
+    c->dirty = true;
+  }
+  if (out && c->h.dbg) {
+    PBX_CUDA_CHECK(cudaMemcpyAsync(out, c->h.dbg, (size_t)c->grid_blocks * 16 * sizeof(uint64_t),
+                                   cudaMemcpyDeviceToHost, st));
+    PBX_CUDA_CHECK(cudaStreamSynchronize(st));
   }
   return 0;
 }

@@ -24,8 +24,10 @@ struct PbxSparseDev {
   uint32_t* serve_cnt;  // [nranks] keys served for each requester in the last pull
   uint32_t* mail_row;   // [nranks*cap] table row of every served key (reused by push)
   float* push_acc;      // [nranks*cap*push_stride] local merge buffer
+  uint8_t* occ_rep;     // [max_keys] 1 = this occurrence is the representative (first claimer) of its unique key in the last pull
   uint64_t* epoch;      // barrier epoch counter
   int* status;          // 0 ok, 1 mailbox overflow, 2 barrier timeout
+  uint64_t* dbg;        // optional [grid, 16] per-CTA phase-end stamps (globaltimer), NULL = off
   int q3_tile_rows;     // push Q3: rows per warp tile (0 = generic per-thread path)
   int q3_warp_words;    // push Q3: shared-memory words per warp
   PbxTableView table;

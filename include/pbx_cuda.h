@@ -64,6 +64,8 @@ int pbx_sparse_status(void* ctx, int* status, int reset, pbx_stream_t stream);
  * memory (every push enqueues one).  Lets the trainer fail at the NEXT step after a mailbox
  * overflow / barrier timeout without synchronising. */
 int pbx_sparse_status_peek(void* ctx);
+/* diagnosis: per-CTA phase-end timestamps of the last pull / push (benchmarks/micro.py --what imbalance) */
+int pbx_sparse_debug_stamps(void* ctx, int on, uint64_t* out, int* grid_out, pbx_stream_t stream);
 /* Copies the 16 phase-boundary globaltimer stamps (ns) of the last pull (0..5) and push (8..12); synchronises. */
 int pbx_sparse_phase_times(void* ctx, uint64_t* out16, pbx_stream_t stream);
 int pbx_sparse_pull(void* ctx, const uint64_t* d_keys, int64_t n, uint32_t* d_restore, pbx_stream_t stream);
