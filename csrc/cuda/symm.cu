@@ -110,6 +110,33 @@ k_symm_collective(const PbxSymmDev* __restrict__ ctxs, int nvr, int64_t off, int
   if (lb == 0 && threadIdx.x == 0) *c.epoch = e0 + 2;
 }
 
+// data_norm(sync_stats): the three batch-statistics vectors of every rank sit in the symmetric
+// region at [off, off + 3*C); every rank sums them over all peers with P2P loads and applies the
+// decayed summary update to its own (plain, local) summary vectors — barrier, reduce, update,
+// barrier in ONE launch.  The reference does 3 ncclAllReduce calls and a separate KernelUpdateParam
+// (data_norm_op.cu:203-231, :90-110).
+template <bool EMU>
+__global__ void __launch_bounds__(256, 1)
+k_symm_stat_update(const PbxSymmDev* __restrict__ ctxs, int nvr, int64_t off, int C, float scale, float decay,
+                   float* const* __restrict__ summaries /* [nvr][3] */) {
+  cg::grid_group grid = cg::this_grid();
+  const int bpr = gridDim.x / nvr;
+  const int vr = blockIdx.x / bpr;
+  const int lb = blockIdx.x % bpr;
+  const PbxSymmDev& c = ctxs[vr];
+  const int R = c.nranks;
+  const uint64_t e0 = *c.epoch;
+  symm_barrier<EMU>(grid, c, e0 + 1, lb == 0);
+  for (int64_t i = (int64_t)lb * blockDim.x + threadIdx.x; i < 3 * (int64_t)C; i += (int64_t)bpr * blockDim.x) {
+    float acc = 0.f;
+    for (int p = 0; p < R; ++p) acc += __ldcg(c.data[(c.rank + p) % R] + off + i);
+    float* dst = summaries[vr * 3 + (int)(i / C)] + (i % C);
+    *dst = *dst * decay + acc * scale;
+  }
+  symm_barrier<EMU>(grid, c, e0 + 2, lb == 0);   // nobody refills its statistics while a peer still reads them
+  if (lb == 0 && threadIdx.x == 0) *c.epoch = e0 + 2;
+}
+
 void symm_bind(PbxSymm* s, int p, void* base) {
   s->peer_base[p] = base;
   s->h.flags[p] = (uint64_t*)base;
@@ -149,6 +176,7 @@ int pbx_symm_destroy(void* h) {
   cudaFree(s->base);
   cudaFree(s->h.epoch);
   cudaFree(s->d);
+  cudaFree(s->stat_ptrs);
   delete s;
   return 0;
 }
@@ -211,6 +239,58 @@ int pbx_symm_collective(void* h, int64_t off, int64_t n, float scale, int op, in
   void* args[] = {(void*)&d, (void*)&nvr, (void*)&off, (void*)&n, (void*)&scale, (void*)&op, (void*)&root};
   PBX_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_symm_collective<false>, dim3(blocks), dim3(512), args, 0, st));
   pbx_note_launch(1);
+  return 0;
+}
+
+// summaries = summaries * decay + scale * sum over ranks of the statistics at [off, off + 3*C) of the
+// symmetric region; d_size / d_sum / d_sqsum are this rank's (ordinary) summary vectors of length C.
+int pbx_symm_stat_update(void* h, int64_t off, int C, float scale, float decay, float* d_size, float* d_sum,
+                         float* d_sqsum, cudaStream_t st) {
+  PbxSymm* s = (PbxSymm*)h;
+  PBX_REQUIRE(C > 0 && (uint64_t)(off + 3 * (int64_t)C) * 4 <= s->bytes - s->data_off,
+              "stat update range exceeds the symmetric region");
+  if (s->dirty) {
+    PBX_CUDA_CHECK(cudaMemcpyAsync(s->d, &s->h, sizeof(PbxSymmDev), cudaMemcpyHostToDevice, st));
+    PBX_CUDA_CHECK(cudaStreamSynchronize(st));
+    s->dirty = false;
+  }
+  if (!s->stat_ptrs) PBX_CUDA_CHECK(cudaMalloc(&s->stat_ptrs, 3 * sizeof(float*)));
+  float* hp[3] = {d_size, d_sum, d_sqsum};
+  if (memcmp(hp, s->stat_ptrs_host, sizeof(hp)) != 0) {
+    memcpy(s->stat_ptrs_host, hp, sizeof(hp));
+    PBX_CUDA_CHECK(cudaMemcpyAsync(s->stat_ptrs, s->stat_ptrs_host, sizeof(hp), cudaMemcpyHostToDevice, st));
+  }
+  const PbxSymmDev* d = s->d;
+  int nvr = 1;
+  float* const* sp = s->stat_ptrs;
+  int blocks = (3 * C + 255) / 256;
+  if (blocks > 16) blocks = 16;
+  void* args[] = {(void*)&d, (void*)&nvr, (void*)&off, (void*)&C, (void*)&scale, (void*)&decay, (void*)&sp};
+  PBX_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_symm_stat_update<false>, dim3(blocks), dim3(256), args, 0, st));
+  pbx_note_launch(1);
+  return 0;
+}
+
+// the same for all virtual ranks of a same-process group in one launch (tests): summaries[r*3 + j]
+int pbx_symm_stat_update_emu(void* const* hs, int nranks, int64_t off, int C, float scale, float decay,
+                             float* const* summaries, cudaStream_t st) {
+  std::vector<PbxSymmDev> hv(nranks);
+  for (int r = 0; r < nranks; ++r) hv[r] = ((PbxSymm*)hs[r])->h;
+  PbxSymmDev* d = nullptr;
+  float** sp = nullptr;
+  PBX_CUDA_CHECK(cudaMalloc(&d, sizeof(PbxSymmDev) * nranks));
+  PBX_CUDA_CHECK(cudaMalloc(&sp, sizeof(float*) * 3 * nranks));
+  PBX_CUDA_CHECK(cudaMemcpy(d, hv.data(), sizeof(PbxSymmDev) * nranks, cudaMemcpyHostToDevice));
+  PBX_CUDA_CHECK(cudaMemcpy(sp, summaries, sizeof(float*) * 3 * nranks, cudaMemcpyHostToDevice));
+  const PbxSymmDev* dc = d;
+  float* const* spc = sp;
+  int bpr = 2;
+  void* args[] = {(void*)&dc, (void*)&nranks, (void*)&off, (void*)&C, (void*)&scale, (void*)&decay, (void*)&spc};
+  cudaError_t e = cudaLaunchCooperativeKernel((void*)k_symm_stat_update<true>, dim3(bpr * nranks), dim3(256), args, 0, st);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFree(d);
+  cudaFree(sp);
+  PBX_CUDA_CHECK(e);
   return 0;
 }
 

@@ -19,5 +19,7 @@ struct PbxSymm {
   size_t bytes, data_off;
   void* peer_base[PBX_MAX_RANKS];
   bool opened[PBX_MAX_RANKS];
+  float** stat_ptrs;            // device [3]: summary vectors of the last pbx_symm_stat_update
+  float* stat_ptrs_host[3];
 };
 

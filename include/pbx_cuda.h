@@ -213,6 +213,43 @@ int pbx_symm_collective(void* symm, int64_t off, int64_t n, float scale, int op,
 int pbx_symm_collective_emu(void* const* symms, int nranks, int64_t off, int64_t n, float scale, int op,
                             int root, pbx_stream_t stream);
 
+/* ---- remaining CTR operator family (csrc/cuda/ctr_ops.cu) ----
+ * reference: rank_attention.cu.h:28-195 + rank_attention_op.cu:30-392; scaled_int8fc_op.cu:38-72;
+ * fused/fused_seqpool_cvm_with_pcoc_op.cu:36-294; fused/fused_concat_op.cu:34-258;
+ * fused/fused_seq_tensor_op.cu:14-147; cross_norm_hadamard.cu.h:44-225. */
+int pbx_rank_attention_expand(const float* d_x, int ldx, const int32_t* d_rank_offset, int N, int C, int R,
+                              void* d_out_bf16, int ldo, void* d_out_t_bf16, int ldt, pbx_stream_t stream);
+int pbx_rank_attention_dx(const float* d_dA, int lda, const int32_t* d_rank_offset, int N, int C, int R, float* d_dx,
+                          int ldx, pbx_stream_t stream);
+int pbx_int8_quant_bf16(const float* d_x, int ldx, int M, int K, float expand, float clip, float int8_range,
+                        void* d_out, int ldo, void* d_out_t, int ldt, pbx_stream_t stream);
+int pbx_seqpool_pcoc_fwd(const float* d_x, int x_stride, const int32_t* d_lod, int B, int S, int H, int use_cvm,
+                         int used, int mx, int need_filter, int quant_ratio, float pad_value, float show_coeff,
+                         float clk_coeff, float threshold, float* d_out, int out_stride, pbx_stream_t stream);
+int pbx_seqpool_pcoc_bwd(const float* d_dout, int out_stride, const float* d_cvm, int cvm_ld, const float* d_q,
+                         const int32_t* d_lod, int B, int S, int H, int use_cvm, int used, int mx, float* d_dx,
+                         int dx_stride, pbx_stream_t stream);
+int pbx_fused_concat(const float* const* d_in, float* const* d_din, const int* ld, const int* width, int n_in, int B,
+                     int start, int len, float* d_out_or_dout, int ldo, int backward, pbx_stream_t stream);
+int pbx_seqpool_concat_fwd(const float* d_x0, int ld0, int off0, int d0, const float* d_x1, int ld1, int off1, int d1,
+                           const int32_t* d_lod, int B, int S, float* d_out, int ldo, pbx_stream_t stream);
+int pbx_seqpool_concat_bwd(const float* d_dout, int ldo, const int32_t* d_lod, int B, int S, float* d_dx0, int ld0,
+                           int w0, int off0, int d0, float* d_dx1, int ld1, int w1, int off1, int d1,
+                           pbx_stream_t stream);
+int pbx_fused_seq_tensor(const float* d_x, const float* d_ad, int ins, int bc, int slot_num, int max_length, int dim,
+                         int ad_slot_num, int ad_slot_offset, float* d_din, float* d_sess, float* d_side,
+                         float* d_mask, pbx_stream_t stream);
+int pbx_cross_hadamard_fwd(const float* d_x, int ldx, int B, int fields, int dim, float* d_y, int ldy,
+                           pbx_stream_t stream);
+int pbx_cross_hadamard_bwd(const float* d_x, int ldx, const float* d_gy, int ldy, int B, int fields, int dim,
+                           float* d_dx, int lddx, pbx_stream_t stream);
+/* data_norm(sync_stats): 3 stat vectors reduced over the ranks + decayed summary update in one launch
+ * (reference: 3 ncclAllReduce + KernelUpdateParam, data_norm_op.cu:203-231, :90-110) */
+int pbx_symm_stat_update(void* symm, int64_t off, int C, float scale, float decay, float* d_size, float* d_sum,
+                         float* d_sqsum, pbx_stream_t stream);
+int pbx_symm_stat_update_emu(void* const* symms, int nranks, int64_t off, int C, float scale, float decay,
+                             float* const* summaries, pbx_stream_t stream);
+
 #ifdef __cplusplus
 }
 #endif

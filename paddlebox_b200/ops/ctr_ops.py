@@ -1,20 +1,92 @@
-"""The remaining CTR operator family of the reference, expressed on PyTorch tensors.
+"""The remaining CTR operator family of the reference.
 
-These ops are not on the hot path of the headline models; they are written as compositions
-of PyTorch ops (differentiable through autograd, CPU and CUDA), with the GEMM-shaped ones
-able to route through the tcgen05 kernel.  Each cites the reference op it restates.
+On CUDA tensors every op here runs on this repo's kernels: the GEMM-shaped ones (rank_attention,
+batch_fc, scaled_fc, scaled_int8fc) on the tcgen05 GEMM through ``ops/tc_linear.py`` with their
+operands built by ``csrc/cuda/ctr_ops.cu``; the memory-bound ones (with_pcoc, fused_concat,
+fused_seqpool_concat, fused_seq_tensor, cross_norm_hadamard) as single-pass kernels of the same
+file.  The ``*_torch`` functions are the same ops as plain PyTorch compositions: the CPU path
+(no GPU in the process) and the oracles of the GPU tests.  Each cites the reference op it restates.
 """
 from __future__ import annotations
+
+import ctypes as C
 
 import torch
 import torch.nn as nn
 
+from .. import _native as N
 from . import functional as F
+
+
+def _on_gpu(*ts) -> bool:
+    return any(t is not None and torch.is_tensor(t) and t.is_cuda for t in ts)
 
 
 # ---------------------------------------------------------------- rank_attention
 def rank_attention(x: torch.Tensor, rank_offset: torch.Tensor, rank_param: torch.Tensor, max_rank: int = 3,
                    max_size: int = 0) -> torch.Tensor:
+    """PV-aware attention over the ads of one page view (see ``rank_attention_torch`` for the contract).
+
+    CUDA: ``k_rank_expand`` gathers the instance's page-view rows into a block-sparse operand
+    ``A[i, (own_i*R + rank_k)*C : +C] = x[index_k]`` (bf16, plus its transpose), so that the whole op is
+    ONE tcgen05 GEMM ``A[N, R*R*C] . rank_param[R*R*C, out]`` instead of the reference's N per-instance
+    products through BatchedGEMM (rank_attention_op.cu:110); the weight gradient is ``A^T . dOut`` on the
+    same kernel and the input gradient is scattered back by ``k_rank_dx``."""
+    if not _on_gpu(x):
+        return rank_attention_torch(x, rank_offset, rank_param, max_rank, max_size)
+    return _RankAttention.apply(x.contiguous().float(), rank_offset.contiguous().int(), rank_param, max_rank)
+
+
+class _RankAttention(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, ro, param, R):
+        from .tc_linear import _bf16_pair, _LinearTC
+        Nn, Cc = x.shape
+        K = R * R * Cc
+        assert param.shape[0] == K, f"rank_param has {param.shape[0]} rows, expected max_rank^2 * C = {K}"
+        pad8 = lambda v: (v + 7) // 8 * 8                                   # noqa: E731
+        ab = torch.empty(Nn, pad8(K), dtype=torch.bfloat16, device=x.device)
+        at = torch.zeros(K, pad8(Nn), dtype=torch.bfloat16, device=x.device)
+        if pad8(K) != K:
+            ab[:, K:].zero_()
+        N.check(N.cuda().pbx_rank_attention_expand(N.ptr(x), x.stride(0), N.ptr(ro), Nn, Cc, R, N.ptr(ab),
+                                                   ab.stride(0), N.ptr(at), at.stride(0), N.stream_ptr()),
+                "pbx_rank_attention_expand")
+        ctx.meta = (Nn, Cc, R, K)
+        ctx.save_for_backward(ro, ab, at, param)
+        from .mlp import cast_transpose_multi, gemm_bf16_tn
+        wb, wt = _bf16_pair(param)
+        cast_transpose_multi([(param.detach().float().contiguous(), wb, wt)])
+        ctx.wb = wb
+        out = torch.empty(Nn, param.shape[1], dtype=torch.float32, device=x.device)
+        gemm_bf16_tn(ab, wt, Nn, param.shape[1], K, out_f32=out)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        from .mlp import cast_transpose_multi, gemm_bf16_tn
+        from .tc_linear import _bf16_pair
+        ro, ab, at, param = ctx.saved_tensors
+        Nn, Cc, R, K = ctx.meta
+        O = param.shape[1]
+        g = g.contiguous().float()
+        gb, gt = _bf16_pair(g)
+        cast_transpose_multi([(g, gb, gt)])
+        dx = dparam = None
+        if ctx.needs_input_grad[2]:
+            dparam = torch.empty(K, O, dtype=torch.float32, device=g.device)
+            gemm_bf16_tn(at, gt, K, O, Nn, out_f32=dparam)                     # A^T [K, N] . dOut^T [O, N]^T
+        if ctx.needs_input_grad[0]:
+            dA = torch.empty(Nn, K, dtype=torch.float32, device=g.device)
+            gemm_bf16_tn(gb, ctx.wb, Nn, K, O, out_f32=dA)                      # dOut [N, O] . param [K, O]^T
+            dx = torch.zeros(Nn, Cc, dtype=torch.float32, device=g.device)
+            N.check(N.cuda().pbx_rank_attention_dx(N.ptr(dA), dA.stride(0), N.ptr(ro), Nn, Cc, R, N.ptr(dx),
+                                                   dx.stride(0), N.stream_ptr()), "pbx_rank_attention_dx")
+        return dx, None, dparam, None
+
+
+def rank_attention_torch(x: torch.Tensor, rank_offset: torch.Tensor, rank_param: torch.Tensor, max_rank: int = 3,
+                         max_size: int = 0) -> torch.Tensor:
     """PV-aware attention over the ads of one page view.
 
     ``rank_offset`` [N, 2*max_rank+1] int: col 0 = own rank (1-based, <= 0: invalid), then for
@@ -100,23 +172,28 @@ def batch_fc(x: torch.Tensor, w: torch.Tensor, b: torch.Tensor, act: str | None 
       block k of the output is ``x``'s block k times ``w``'s block k;
     * ``transpose_weight`` (needs ``batchcount``): ``x`` [bc, ins, in], ``w`` [in, bc*out], ``b`` [1, bc*out]
       -> [bc, ins, out]."""
+    # every layout is a batch of independent [ins, in] x [in, out] products: on CUDA they run as grouped
+    # launches of the tcgen05 GEMM (bias and ReLU in the epilogue), on CPU through torch.baddbmm
+    def bmm(xb, wb, bb):
+        if _on_gpu(xb):
+            from .tc_linear import grouped_linear_tc
+            return grouped_linear_tc(xb.float(), wb.float(), bb.float(), relu=(act == "relu"))
+        y_ = torch.baddbmm(bb[:, None, :], xb, wb)
+        return torch.relu(y_) if act == "relu" else y_
+
     if transpose_weight:
         if batchcount <= 0:
             raise ValueError("with transpose_weight, batchcount should be > 0")
         bc, out = batchcount, w.shape[1] // batchcount
         wb = w.view(w.shape[0], bc, out).permute(1, 0, 2)                       # [bc, in, out]
-        y = torch.baddbmm(b.reshape(bc, 1, out), x, wb)
-    elif batchcount > 0:
+        return bmm(x, wb, b.reshape(bc, out))
+    if batchcount > 0:
         bc, ins = batchcount, x.shape[0]
         fin, out = x.shape[1] // bc, w.shape[1] // bc
         xb = x.view(ins, bc, fin).permute(1, 0, 2)                              # [bc, ins, in]
         wb = w.view(fin, bc, out).permute(1, 0, 2)                              # [bc, in, out]
-        y = torch.baddbmm(b.reshape(bc, 1, out), xb, wb).permute(1, 0, 2).reshape(ins, bc * out)
-    else:
-        y = torch.baddbmm(b[:, None, :], x, w)
-    if act == "relu":
-        y = torch.relu(y)
-    return y
+        return bmm(xb, wb, b.reshape(bc, out)).permute(1, 0, 2).reshape(ins, bc * out)
+    return bmm(x, w, b)
 
 
 # ---------------------------------------------------------------- scaled_fc
@@ -133,6 +210,8 @@ def scaled_fc(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, input_scale_
     is ``dout * grad_scale / input_scale`` and the results are divided by ``grad_scale``.  The reference rounds
     to fp16; here to bf16, the tcgen05 kernel's operand type (fp32 accumulate)."""
     s_in, s_b, s_g = float(input_scale_factor), float(bias_scale_factor), float(grad_scale_factor)
+    if _on_gpu(x):
+        return _ScaledFC.apply(x.float(), w.float(), bias.float(), s_in, s_b, s_g)
 
     def r16(t):
         return t.to(torch.bfloat16).float()
@@ -152,6 +231,43 @@ def scaled_fc(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, input_scale_
             dw = s_in * (r16(x).t() @ g16) / s_g
             return dx, dw, g.sum(0)
     return _Fn.apply(x, w, bias)
+
+
+class _ScaledFC(torch.autograd.Function):
+    """scaled_fc on the tcgen05 GEMM: operands rounded to bf16 by one cast launch, the scale factors in the
+    epilogue (``alpha`` and the bias factor), forward / dX / dW each one GEMM."""
+
+    @staticmethod
+    def forward(ctx, x, w, bias, s_in, s_b, s_g):
+        from .mlp import cast_transpose_multi, gemm_bf16_tn
+        from .tc_linear import _bf16_pair
+        M, K = x.shape
+        Nn = w.shape[1]
+        xb, xt = _bf16_pair(x)
+        wb, wt = _bf16_pair(w)
+        cast_transpose_multi([(x.contiguous(), xb, xt), (w.contiguous(), wb, wt)])
+        y = torch.empty(M, Nn, dtype=torch.float32, device=x.device)
+        # (s_in * (x16 . w16) + s_b * bias16) / s_in
+        b_eff = bias.reshape(-1).to(torch.bfloat16).float() * (s_b / s_in)
+        gemm_bf16_tn(xb, wt, M, Nn, K, bias=b_eff, out_f32=y, alpha=1.0)
+        ctx.save_for_backward(xt, wb)
+        ctx.meta = (M, K, Nn, s_in, s_g)
+        return torch.where(torch.isinf(y), torch.full_like(y, float("nan")), y)
+
+    @staticmethod
+    def backward(ctx, g):
+        from .mlp import cast_transpose_multi, gemm_bf16_tn
+        from .tc_linear import _bf16_pair
+        xt, wb = ctx.saved_tensors
+        M, K, Nn, s_in, s_g = ctx.meta
+        gs = (g * (s_g / s_in)).contiguous()               # the operand the reference rounds to 16 bits
+        gb, gt = _bf16_pair(gs)
+        cast_transpose_multi([(gs, gb, gt)])
+        dx = torch.empty(M, K, dtype=torch.float32, device=g.device)
+        dw = torch.empty(K, Nn, dtype=torch.float32, device=g.device)
+        gemm_bf16_tn(gb, wb, M, K, Nn, out_f32=dx, alpha=s_in / s_g)
+        gemm_bf16_tn(xt, gt, K, Nn, M, out_f32=dw, alpha=s_in / s_g)
+        return dx, dw, g.sum(0), None, None, None
 
 
 def _int8_quant(v: torch.Tensor, expand: float, clip: float, int8_range: float) -> torch.Tensor:
@@ -174,6 +290,11 @@ def scaled_int8fc(x, w, bias, input_scale_factor=1.0, bias_scale_factor=1.0, gra
     product is formed in fp32, which is exact for these magnitudes."""
     in_int = 2.0 * input_clip_factor / int8_range
     w_int = 2.0 * weight_clip_factor / int8_range
+    if _on_gpu(x):
+        scale = in_int / (input_expand_factor * weight_expand_factor) * (w_int if dequant_weights else 1.0)
+        return _ScaledInt8FC.apply(x.float(), w.float(), bias.float(), float(input_expand_factor),
+                                   float(input_clip_factor), float(weight_expand_factor), float(weight_clip_factor),
+                                   float(int8_range), float(scale))
 
     class _Fn(torch.autograd.Function):
         @staticmethod
@@ -193,7 +314,77 @@ def scaled_int8fc(x, w, bias, input_scale_factor=1.0, bias_scale_factor=1.0, gra
     return _Fn.apply(x, w, bias)
 
 
+class _ScaledInt8FC(torch.autograd.Function):
+    """``k_int8_quant`` writes both operands as integer-valued bf16 (|q| <= 128: exact), the tcgen05 GEMM forms
+    the integer product in fp32 (exact while in_dim * 128^2 < 2^24) and applies the rescale as ``alpha`` and the
+    bias in its epilogue.  Backward: the plain FC gradient on the un-quantised operands (straight-through), each
+    product one bf16 GEMM."""
+
+    @staticmethod
+    def forward(ctx, x, w, bias, xe, xc, we, wc, rng, scale):
+        from .mlp import cast_transpose_multi, gemm_bf16_tn
+        from .tc_linear import _bf16_pair
+        M, K = x.shape
+        Nn = w.shape[1]
+        xq, _ = _bf16_pair(x, True, False)
+        _, wqt = _bf16_pair(w, False, True)
+        lib = N.cuda()
+        N.check(lib.pbx_int8_quant_bf16(N.ptr(x), x.stride(0), M, K, C.c_float(xe), C.c_float(xc), C.c_float(rng),
+                                        N.ptr(xq), xq.stride(0), None, 0, N.stream_ptr()), "pbx_int8_quant_bf16")
+        N.check(lib.pbx_int8_quant_bf16(N.ptr(w), w.stride(0), K, Nn, C.c_float(we), C.c_float(wc), C.c_float(rng),
+                                        None, 0, N.ptr(wqt), wqt.stride(0), N.stream_ptr()), "pbx_int8_quant_bf16")
+        y = torch.empty(M, Nn, dtype=torch.float32, device=x.device)
+        gemm_bf16_tn(xq, wqt, M, Nn, K, bias=bias.reshape(-1).contiguous(), out_f32=y, alpha=scale)
+        # operands of the straight-through backward
+        _, xt = _bf16_pair(x, False, True)
+        wb, _ = _bf16_pair(w, True, False)
+        cast_transpose_multi([(x.contiguous(), None, xt), (w.contiguous(), wb, None)])
+        ctx.save_for_backward(xt, wb)
+        ctx.meta = (M, K, Nn)
+        return y
+
+    @staticmethod
+    def backward(ctx, g):
+        from .mlp import cast_transpose_multi, gemm_bf16_tn
+        from .tc_linear import _bf16_pair
+        xt, wb = ctx.saved_tensors
+        M, K, Nn = ctx.meta
+        g = g.contiguous()
+        gb, gt = _bf16_pair(g)
+        cast_transpose_multi([(g, gb, gt)])
+        dx = torch.empty(M, K, dtype=torch.float32, device=g.device)
+        dw = torch.empty(K, Nn, dtype=torch.float32, device=g.device)
+        gemm_bf16_tn(gb, wb, M, K, Nn, out_f32=dx)
+        gemm_bf16_tn(xt, gt, K, Nn, M, out_f32=dw)
+        return dx, dw, g.sum(0), None, None, None, None, None, None
+
+
 # ---------------------------------------------------------------- cross_norm_hadamard
+class _CrossHadamard(torch.autograd.Function):
+    """[a, b] field pairs -> [a, b, a*b, <a, b>] blocks; one kernel forward, one backward (ctr_ops.cu)."""
+
+    @staticmethod
+    def forward(ctx, x, f, d):
+        x = x.contiguous()
+        B = x.shape[0]
+        y = torch.empty(B, f * (3 * d + 1), dtype=torch.float32, device=x.device)
+        N.check(N.cuda().pbx_cross_hadamard_fwd(N.ptr(x), x.stride(0), B, f, d, N.ptr(y), y.stride(0), N.stream_ptr()),
+                "pbx_cross_hadamard_fwd")
+        ctx.save_for_backward(x)
+        ctx.meta = (f, d)
+        return y
+
+    @staticmethod
+    def backward(ctx, gy):
+        (x,) = ctx.saved_tensors
+        f, d = ctx.meta
+        gy = gy.contiguous()
+        dx = torch.empty_like(x)
+        N.check(N.cuda().pbx_cross_hadamard_bwd(N.ptr(x), x.stride(0), N.ptr(gy), gy.stride(0), x.shape[0], f, d,
+                                                N.ptr(dx), dx.stride(0), N.stream_ptr()), "pbx_cross_hadamard_bwd")
+        return dx, None, None
+
+
 class CrossNormHadamard(nn.Module):
     """For ``fields_num`` field pairs (a_i, b_i) of width ``embed_dim`` laid side by side in the input
     (``[a_0, b_0, a_1, b_1, ...]``), emit per pair the block ``[a_i, b_i, a_i*b_i, <a_i, b_i>]`` —
@@ -211,6 +402,8 @@ class CrossNormHadamard(nn.Module):
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         B = x.shape[0]
         f, d = self.fields_num, self.embed_dim
+        if x.is_cuda:                                       # expansion kernel, then the data_norm kernels
+            return self.norm(_CrossHadamard.apply(x.float(), f, d))
         pairs = x.view(B, f, 2, d)
         a, b = pairs[:, :, 0], pairs[:, :, 1]
         had = a * b
@@ -222,12 +415,50 @@ class CrossNormHadamard(nn.Module):
 def fused_concat(inputs, start_index: int = 0, length: int = -1, axis: int = 1) -> torch.Tensor:
     """Column slice ``[start, start+length)`` of every input, concatenated (reference
     fused_concat_op.cu:34-258)."""
+    inputs = list(inputs)
+    s0 = max(start_index, 0)                          # the layer clamps a negative start to 0 (nn.py:2822)
+    if _on_gpu(*inputs) and axis == 1 and len(inputs) <= 64 and all(t.dim() == 2 for t in inputs) and \
+            (length > 0 or len({t.shape[1] for t in inputs}) == 1):
+        ln = length if length > 0 else inputs[0].shape[1] - s0
+        return _FusedConcat.apply(s0, ln, *[t.float() for t in inputs])
     outs = []
     for t in inputs:
-        s = max(start_index, 0)                       # the layer clamps a negative start to 0 (nn.py:2822)
+        s = s0
         e = t.shape[1] if length < 0 else s + length
         outs.append(t[:, s:e])
     return torch.cat(outs, dim=axis)
+
+
+class _FusedConcat(torch.autograd.Function):
+    """One launch gathers the column slice of up to 64 inputs into the output; one launch splits the
+    gradient back (zero outside the slice) — fused_concat_op.cu:34-258."""
+
+    @staticmethod
+    def _tables(ts):
+        n = len(ts)
+        return ((C.c_void_p * n)(*[t.data_ptr() for t in ts]), (C.c_int * n)(*[t.stride(0) for t in ts]),
+                (C.c_int * n)(*[t.shape[1] for t in ts]))
+
+    @staticmethod
+    def forward(ctx, start, length, *xs):
+        xs = [t.contiguous() for t in xs]
+        B, n = xs[0].shape[0], len(xs)
+        out = torch.empty(B, n * length, dtype=torch.float32, device=xs[0].device)
+        ptrs, ld, wd = _FusedConcat._tables(xs)
+        N.check(N.cuda().pbx_fused_concat(ptrs, None, ld, wd, n, B, start, length, N.ptr(out), out.stride(0), 0,
+                                          N.stream_ptr()), "pbx_fused_concat")
+        ctx.meta = (start, length, [tuple(t.shape) for t in xs])
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        start, length, shapes = ctx.meta
+        g = g.contiguous()
+        dxs = [torch.empty(sh, dtype=torch.float32, device=g.device) for sh in shapes]
+        ptrs, ld, wd = _FusedConcat._tables(dxs)
+        N.check(N.cuda().pbx_fused_concat(None, ptrs, ld, wd, len(dxs), shapes[0][0], start, length, N.ptr(g),
+                                          g.stride(0), 1, N.stream_ptr()), "pbx_fused_concat(bwd)")
+        return (None, None, *dxs)
 
 
 def _partial_range(width: int, start_index: int, length: int):
@@ -275,6 +506,14 @@ def fused_seqpool_concat(inputs, num_slots: int, offsets=None, dims=None, lod: t
         raise ValueError("fused_seqpool_concat takes exactly two input groups")
     assert lod is not None and batch_size is not None, "sequence inputs need lod and batch_size"
     B, S = batch_size, num_slots
+    if _on_gpu(inputs[0]):
+        geo = []
+        for g, x in enumerate(inputs):
+            start = max(0, offsets[g]) if isinstance(offsets, (list, tuple)) and g < len(offsets) else 0
+            dim = dims[g] if isinstance(dims, (list, tuple)) and g < len(dims) else 0
+            geo.append((start, dim if dim > 0 else x.shape[1] - start))
+        return _SeqpoolConcat.apply(inputs[0].float(), inputs[1].float(), lod.int(), B, S, geo[0][0], geo[0][1],
+                                    geo[1][0], geo[1][1])
     lens = (lod[1:] - lod[:-1]).long()
     n = int(lod[-1])
     bag = torch.repeat_interleave(torch.arange(S * B, device=lod.device), lens, output_size=n)
@@ -287,6 +526,34 @@ def fused_seqpool_concat(inputs, num_slots: int, offsets=None, dims=None, lod: t
         pooled = torch.zeros(S * B, dim, dtype=x.dtype, device=x.device).index_add_(0, bag, x[:n, start:start + dim])
         parts.append(pooled.view(S, B, dim))
     return torch.cat(parts, 2).permute(1, 0, 2).reshape(B, -1)
+
+
+class _SeqpoolConcat(torch.autograd.Function):
+    """Sum-pool two per-key groups by one lod and lay their column ranges side by side, in one kernel;
+    the backward writes every key row of both groups (zero outside the ranges) in one kernel."""
+
+    @staticmethod
+    def forward(ctx, x0, x1, lod, B, S, off0, d0, off1, d1):
+        x0, x1, lod = x0.contiguous(), x1.contiguous(), lod.contiguous()
+        out = torch.empty(B, S * (d0 + d1), dtype=torch.float32, device=x0.device)
+        N.check(N.cuda().pbx_seqpool_concat_fwd(N.ptr(x0), x0.stride(0), off0, d0, N.ptr(x1), x1.stride(0), off1, d1,
+                                                N.ptr(lod), B, S, N.ptr(out), out.stride(0), N.stream_ptr()),
+                "pbx_seqpool_concat_fwd")
+        ctx.save_for_backward(lod)
+        ctx.meta = (B, S, off0, d0, off1, d1, tuple(x0.shape), tuple(x1.shape))
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (lod,) = ctx.saved_tensors
+        B, S, off0, d0, off1, d1, sh0, sh1 = ctx.meta
+        g = g.contiguous()
+        dx0 = torch.zeros(sh0, dtype=torch.float32, device=g.device)     # rows beyond lod[-1] stay zero
+        dx1 = torch.zeros(sh1, dtype=torch.float32, device=g.device)
+        N.check(N.cuda().pbx_seqpool_concat_bwd(N.ptr(g), g.stride(0), N.ptr(lod), B, S, N.ptr(dx0), dx0.stride(0),
+                                                sh0[1], off0, d0, N.ptr(dx1), dx1.stride(0), sh1[1], off1, d1,
+                                                N.stream_ptr()), "pbx_seqpool_concat_bwd")
+        return dx0, dx1, None, None, None, None, None, None, None
 
 
 def fused_seq_tensor(x: torch.Tensor, ad_input: torch.Tensor, batch_count: int, max_length: int, slot_num: int,
@@ -307,6 +574,18 @@ def fused_seq_tensor(x: torch.Tensor, ad_input: torch.Tensor, batch_count: int, 
     * ``ad_slot_session`` ``[..., ad_slot_num * dim]`` = the sequence values of the ad slots."""
     ins = x.shape[0]
     bc, L, D, an = batch_count, max_length, fea_emb_dim, ad_slot_num
+    if x.is_cuda and not (x.requires_grad or ad_input.requires_grad):
+        # forward-only in the reference too (fused_seq_tensor_op.cc registers no gradient op): one kernel
+        # writes all four outputs; inputs that need gradients take the differentiable composition below
+        xc, ac = x.contiguous().float(), ad_input.contiguous().float()
+        din = torch.empty(bc, ins, L, 4 * an * D, dtype=torch.float32, device=x.device)
+        sess = torch.empty(bc, ins, L, an * D, dtype=torch.float32, device=x.device)
+        side = torch.empty(bc, ins, L, (slot_num - an) * D, dtype=torch.float32, device=x.device)
+        mask = torch.empty(bc, ins, L, dtype=torch.float32, device=x.device)
+        N.check(N.cuda().pbx_fused_seq_tensor(N.ptr(xc), N.ptr(ac), ins, bc, slot_num, L, D, an, ad_slot_offset,
+                                              N.ptr(din), N.ptr(sess), N.ptr(side), N.ptr(mask), N.stream_ptr()),
+                "pbx_fused_seq_tensor")
+        return din, mask.to(x.dtype), side, sess
     seq = x.reshape(ins, bc, slot_num, L, D)
     ad = ad_input.reshape(ins, bc, an, D)
     inp = seq[:, :, ad_slot_offset:ad_slot_offset + an].permute(1, 0, 3, 2, 4)          # [bc, ins, L, an, D]
@@ -365,6 +644,21 @@ class _SeqpoolCVMWithPCOC(torch.autograd.Function):
     def forward(ctx, x, cvm, q_values, lod, B, S, use_cvm, used, mx, pad_value, need_filter, show_coeff, clk_coeff,
                 threshold, quant_ratio):
         H = x.shape[1]
+        if x.is_cuda:                 # single-pass kernel: pool + filter + quant + PCOC transform (ctr_ops.cu)
+            x = x.contiguous().float()
+            lod32 = lod.contiguous().int()
+            E = (2 + 2 * (used - 4) if use_cvm else 0) + (H - mx)
+            out = torch.empty(B, S * E, dtype=torch.float32, device=x.device)
+            N.check(N.cuda().pbx_seqpool_pcoc_fwd(N.ptr(x), x.stride(0), N.ptr(lod32), B, S, H, int(use_cvm), used, mx,
+                                                  int(need_filter), int(quant_ratio), C.c_float(pad_value),
+                                                  C.c_float(show_coeff), C.c_float(clk_coeff), C.c_float(threshold),
+                                                  N.ptr(out), out.stride(0), N.stream_ptr()), "pbx_seqpool_pcoc_fwd")
+            ctx.meta = (B, S, H, x.shape[0], use_cvm, used, mx, E)
+            ctx.gpu = True
+            ctx.save_for_backward(cvm.contiguous().float(), q_values.contiguous().float() if q_values is not None
+                                  else None, lod32)
+            return out
+        ctx.gpu = False
         G = B * S
         lens = (lod[1:] - lod[:-1]).long()
         n = int(lod[-1])
@@ -386,6 +680,7 @@ class _SeqpoolCVMWithPCOC(torch.autograd.Function):
         else:
             out = pooled[:, mx:]
         ctx.meta = (B, S, H, n, use_cvm, used, mx, out.shape[1])
+        ctx.rows = x.shape[0]
         ctx.save_for_backward(cvm, q_values, seg)
         E = out.shape[1]
         return out.view(S, B, E).permute(1, 0, 2).reshape(B, S * E)
@@ -394,6 +689,16 @@ class _SeqpoolCVMWithPCOC(torch.autograd.Function):
     def backward(ctx, dout):
         cvm, q_values, seg = ctx.saved_tensors
         B, S, H, n, use_cvm, used, mx, E = ctx.meta
+        if ctx.gpu:
+            lod32 = seg
+            dout = dout.contiguous()
+            dx = torch.zeros(n, H, dtype=torch.float32, device=dout.device)    # rows beyond lod[-1] stay zero
+            N.check(N.cuda().pbx_seqpool_pcoc_bwd(N.ptr(dout), dout.stride(0), N.ptr(cvm), cvm.stride(0),
+                                                  N.ptr(q_values.reshape(B, used - 4)) if (q_values is not None and
+                                                                                          used > 4) else None,
+                                                  N.ptr(lod32), B, S, H, int(use_cvm), used, mx, N.ptr(dx),
+                                                  dx.stride(0), N.stream_ptr()), "pbx_seqpool_pcoc_bwd")
+            return (dx,) + (None,) * 14
         b_of = seg % B
         dx = torch.zeros(n, H, dtype=dout.dtype, device=dout.device)
         dx[:, :4] = cvm[b_of, :4]                         # show / clk / show2 / clk2 counts ride on the gradient
@@ -401,6 +706,8 @@ class _SeqpoolCVMWithPCOC(torch.autograd.Function):
             dx[:, 4:used] = q_values.reshape(B, used - 4)[b_of]
         d = dout.reshape(B, S, E)[b_of, seg // B]
         dx[:, mx:] = d[:, E - (H - mx):]
+        if ctx.rows > n:                                  # rows of x beyond lod[-1] belong to no bag
+            dx = torch.cat([dx, torch.zeros(ctx.rows - n, H, dtype=dx.dtype, device=dx.device)], 0)
         return (dx,) + (None,) * 14
 
 

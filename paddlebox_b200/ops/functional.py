@@ -151,9 +151,13 @@ class DataNorm(nn.Module):
         self.register_buffer("batch_sum", torch.zeros(num_features))
         self.register_buffer("batch_square_sum", torch.full((num_features,), 1e4))
         self.reduce_fn = None  # set by the trainer: f(tensor[3, C]) -> averaged in place
+        self.stat_sync = None  # set by the trainer on GPUs: f(module, d_size, d_sum, d_sq) = fused reduce + update
 
     def _apply_stats(self, d_size, d_sum, d_sq):
         with torch.no_grad():
+            if self.sync_stats and self.stat_sync is not None:
+                self.stat_sync(self, d_size, d_sum, d_sq)       # one kernel: allreduce of the 3 vectors + decay update
+                return
             stats = torch.stack([d_size, d_sum, d_sq])
             if self.sync_stats and self.reduce_fn is not None:
                 stats = self.reduce_fn(stats)

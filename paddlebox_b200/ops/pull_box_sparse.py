@@ -138,15 +138,43 @@ def split_by_slot(emb: torch.Tensor, batch: SlotBatch, pad_empty: bool = True):
     return outs
 
 
-def pull_box_extended_sparse(batch: SlotBatch, size: int, extend_size: int, box: BoxWrapper | None = None):
-    """(emb [N, size], emb_extend [N, extend_size]): the table row's embedx holds
-    ``embedx_dim = (size - 3) + extend_size`` values; the first part feeds ``emb`` and the tail
-    the expand embedding (reference PullCopyNNCross, box_wrapper.cu:146-268)."""
+def pull_box_extended_sparse(batch: SlotBatch, size: int, extend_size: int, box: BoxWrapper | None = None,
+                             mask=None, offset: int = 0, expand_only: bool = True):
+    """``_pull_box_extended_sparse`` (contrib/layers/nn.py:1678-1750; op pull_box_extended_sparse_op.h:25-193;
+    kernels PullCopyNNCross / PullCopyNNCrossWithEmb, box_wrapper.cu:146-268).
+
+    The table row's embedx holds ``embedx_dim = (size - 3) + extend_size`` values: the first part is the base
+    embedding, the tail the expand embedding.  Returns ``(out, out_extend)``:
+
+    * ``out``  ``[N, size - offset]`` = ``[cvm columns (minus the first ``offset``), base embedx]``;
+    * ``out_extend``: ``expand_only=True`` (layer default) -> ``[N, extend_size]`` the expand embedding alone;
+      ``expand_only=False`` -> ``[N, size - offset + extend_size]`` = base row followed by the expand embedding
+      (the "WithEmb" kernel).
+    * ``mask`` (one int per slot; bit 0 = this slot has an ``Out``, bit 1 = it has an ``OutExtend``): the results
+      become LISTS of per-slot tensors holding only the selected slots, in slot order, exactly like the op's
+      output lists; a slot without a bit gets no tensor and contributes no gradient for that part.
+
+    One pull serves both outputs, and the backward of both flows into the one push (gradient columns that no
+    output selected are zero)."""
     box = box or BoxWrapper.get_instance()
     if size - 3 + extend_size != box.embedx_dim:
         raise ValueError("size - 3 + extend_size must equal the table's embedx_dim")
+    if not 0 <= offset <= 3:
+        raise ValueError("offset skips leading cvm columns: 0..3")
     full = _PullBoxSparse.apply(_anchor(batch.keys.device), box, batch, box.hidden, 0)
-    return full[:, :size], full[:, size:]
+    base = full[:, offset:size]
+    ext = full[:, size:] if expand_only else torch.cat([base, full[:, size:]], 1)
+    if mask is None or len(mask) == 0:
+        return base, ext
+    if len(mask) != batch.num_slots:
+        raise ValueError(f"mask has {len(mask)} entries for {batch.num_slots} slots")
+    outs, outs_ext = [], []
+    for flag, (b0, e0) in zip(mask, batch.slot_ranges()):
+        if flag & 0x01:
+            outs.append(base[b0:e0])
+        if flag & 0x02:
+            outs_ext.append(ext[b0:e0])
+    return outs, outs_ext
 
 
 class _SparseEmbeddingPool(torch.autograd.Function):

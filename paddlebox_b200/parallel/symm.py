@@ -64,6 +64,26 @@ class SymmetricBuffer:
             return
         self.collective("allreduce", offset, numel, scale, stream=stream)
 
+    def stat_update(self, offset: int, width: int, scale: float, decay: float, size: torch.Tensor, total: torch.Tensor,
+                    sqsum: torch.Tensor, stream=None) -> None:
+        """``summary = summary * decay + scale * sum over ranks of stats`` for the three data-norm summaries in one
+        launch: the statistics ``[3, width]`` of every rank sit at ``offset`` of the symmetric region, the summary
+        vectors are ordinary local tensors (csrc/cuda/symm.cu ``k_symm_stat_update``)."""
+        assert size.is_contiguous() and total.is_contiguous() and sqsum.is_contiguous()
+        N.check(N.cuda().pbx_symm_stat_update(self._h, C.c_int64(offset), width, C.c_float(scale), C.c_float(decay),
+                                              N.ptr(size), N.ptr(total), N.ptr(sqsum), N.stream_ptr(stream)),
+                "pbx_symm_stat_update")
+
+    @staticmethod
+    def stat_update_emu(bufs: Sequence["SymmetricBuffer"], offset: int, width: int, scale: float, decay: float,
+                        summaries: Sequence[Sequence[torch.Tensor]]) -> None:
+        """All ranks of an emulated group in one launch (tests): ``summaries[r] = (size, sum, sqsum)`` of rank r."""
+        arr = (C.c_void_p * len(bufs))(*[b._h for b in bufs])
+        flat = [t.data_ptr() for trio in summaries for t in trio]
+        sp = (C.c_void_p * len(flat))(*flat)
+        N.check(N.cuda().pbx_symm_stat_update_emu(arr, len(bufs), C.c_int64(offset), width, C.c_float(scale),
+                                                  C.c_float(decay), sp, N.stream_ptr()), "pbx_symm_stat_update_emu")
+
     def check_status(self) -> None:
         st = C.c_int()
         N.check(N.cuda().pbx_symm_status(self._h, C.byref(st), N.stream_ptr()))

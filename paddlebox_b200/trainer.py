@@ -87,9 +87,22 @@ class CTRTrainer:
                                       self.cfg.dump_interval, self.cfg.dump_thread_num, rank=self.rank)
         self.steps = 0
         self.last_outputs = None
-        for m in model.modules():
-            if getattr(m, "sync_stats", False) and self.world > 1:
-                m.reduce_fn = self._reduce_stats
+        # data_norm(sync_stats): on GPUs of one node the three statistics vectors are reduced over the
+        # ranks and the summaries updated by ONE kernel over symmetric memory (pbx_symm_stat_update);
+        # elsewhere (CPU worlds, several nodes, FLAGS.dense_use_nccl) a torch.distributed allreduce
+        synced = [m for m in model.modules() if getattr(m, "sync_stats", False)]
+        self._stat_symm = None
+        if synced and self.world > 1:
+            fused = self.store.use_symm and self.store.topo is None
+            if fused:
+                from .parallel.symm import SymmetricBuffer
+                width = max(int(m.batch_size.numel()) for m in synced)
+                self._stat_symm = SymmetricBuffer(3 * width + 8, self.rank, self.world, group=self.store.group)
+            for m in synced:
+                if fused:
+                    m.stat_sync = self._sync_stats_fused
+                else:
+                    m.reduce_fn = self._reduce_stats
 
     def dump_main_program(self, path: str | None = None) -> str:
         """``FLAGS_enable_dump_main_program``: the reference writes every device's op list to
@@ -125,6 +138,15 @@ class CTRTrainer:
         local_rank = int(os.environ.get("LOCAL_RANK", "0"))
         mine = cores[local_rank::local_world] or cores
         return list(mine) if set_cpu_affinity(mine) else []
+
+    def _sync_stats_fused(self, m, d_size, d_sum, d_sq) -> None:
+        """summaries = summaries * decay + mean over ranks of the batch statistics, one launch
+        (reference: 3 ncclAllReduce + KernelUpdateParam, data_norm_op.cu:203-231)."""
+        Cn = int(m.batch_size.numel())
+        buf = self._stat_symm.tensor[:3 * Cn].view(3, Cn)
+        torch.stack([d_size.reshape(-1), d_sum.reshape(-1), d_sq.reshape(-1)], out=buf)
+        self._stat_symm.stat_update(0, Cn, 1.0 / self.world, float(m.decay), m.batch_size, m.batch_sum,
+                                    m.batch_square_sum)
 
     def _reduce_stats(self, stats: torch.Tensor) -> torch.Tensor:
         import torch.distributed as dist

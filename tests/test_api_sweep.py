@@ -140,6 +140,17 @@ def test_extended_sparse_rank_attention2_seq_tensor_dedup(box):
     assert ext[0].tolist() == [2.0, 3.0] and ext[1].tolist() == [6.0, 7.0] and torch.equal(ext[0], ext[2])
     with pytest.raises(ValueError):
         pull_box_extended_sparse(batch, size=5, extend_size=3, box=box)
+    # expand_only=False ("WithEmb" kernel): the extended output carries the base row too; offset drops cvm columns
+    emb2, ext2 = pull_box_extended_sparse(batch, size=5, extend_size=2, box=box, offset=2, expand_only=False)
+    assert emb2.shape == (4, 3) and ext2.shape == (4, 5)
+    assert torch.equal(ext2[:, :3], emb2) and torch.equal(ext2[:, 3:], ext) and torch.equal(emb2, emb[:, 2:])
+    # per-slot mask: bit 0 selects Out, bit 1 selects OutExtend (pull_box_extended_sparse_op.h:50-72)
+    b2 = SlotBatch(keys, torch.tensor([0, 1, 2, 3, 4], dtype=torch.int32), 2, 2)      # 2 slots x 2 instances
+    outs, outs_ext = pull_box_extended_sparse(b2, size=5, extend_size=2, box=box, mask=[0x02, 0x03])
+    assert len(outs) == 1 and len(outs_ext) == 2
+    assert torch.equal(outs[0], emb[2:4]) and torch.equal(outs_ext[0], ext[0:2]) and torch.equal(outs_ext[1], ext[2:4])
+    with pytest.raises(ValueError):
+        pull_box_extended_sparse(b2, size=5, extend_size=2, box=box, mask=[1])
     box.end_pass()
     # rank_attention2 = rank_attention
     gen = torch.Generator().manual_seed(1)
