@@ -222,7 +222,7 @@ def bench_sparse(out, flush, keys_per_gpu=125_000_000, dim=16, B=4096, S=26, max
     N.check(N.cuda().pbx_sparse_phase_times(eng._h, ts, N.stream_ptr()))
     t = [int(x) for x in ts]
     names_pull = ["P0 reset", "P1 dedup+route keys", "P2 restore idx", "P2 clear dedup + barrier", "P3 serve rows + barrier"]
-    names_push = ["Q0 zero merge rows", "Q1 merge (seqpool bwd)", "Q2 ship + barrier", "Q3 optimizer"]
+    names_push = ["Q0 init (records go out in k_push_records before this kernel)", "Q1 merge duplicate keys", "Q2 ship + barrier", "Q3 optimizer"]
     ph = {"kernel": "phases_us",
           "pull": {n: round((t[i + 1] - t[i]) / 1e3, 1) for i, n in enumerate(names_pull)},
           "push": {n: round((t[9 + i] - t[8 + i]) / 1e3, 1) for i, n in enumerate(names_push)}}

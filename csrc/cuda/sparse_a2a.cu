@@ -62,6 +62,7 @@ struct PbxPushArgs {
   const PbxSymmDev* dense_ctx;
   int64_t dense_off, dense_n;
   float dense_scale;
+  int q0_done;              // the record phase already ran as its own launch (k_push_records)
 };
 struct PbxPushArgsN { PbxPushArgs a[PBX_MAX_RANKS]; };
 
@@ -138,6 +139,7 @@ k_sparse_pull(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPullArgsN args)
   if (lb == 0 && tid < R) {
     c.send_cnt[tid] = 0;
     c.send_cnt[32 + tid] = 0;     // P3 tile tickets
+    if (tid == 0) c.send_cnt[48] = 0;   // length of the push's duplicate-occurrence list
   }
   {
     const int64_t stride = (int64_t)bpr * PBX_A2A_THREADS;
@@ -241,8 +243,15 @@ k_sparse_pull(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPullArgsN args)
   // ---- P2: occurrence -> unique row, publish counts, clean the dedup table
   {
     const int64_t stride = (int64_t)bpr * PBX_A2A_THREADS;
-    for (int64_t i = (int64_t)lb * PBX_A2A_THREADS + tid; i < a.n; i += stride)
-      a.restore[i] = c.dd_uid[a.restore[i]];
+    const uint32_t tag = (uint32_t)(e0 + 1);
+    for (int64_t i = (int64_t)lb * PBX_A2A_THREADS + tid; i < a.n; i += stride) {
+      const uint32_t uid = c.dd_uid[a.restore[i]];
+      a.restore[i] = uid;
+      // a non-representative occurrence marks its key as "merged from several occurrences": the push
+      // sends single-occurrence records straight to their owner and merges only the marked ones locally
+      if (!c.occ_rep[i]) c.uid_multi[uid] = tag;
+    }
+    if (lb == 0 && tid == 0) c.epoch[5] = tag;
     if (lb == 0 && tid < R) {
       uint32_t n_send = min(c.send_cnt[tid], cap - 1);   // row cap-1 is the overflow row (see P1)
       c.send_cnt[tid] = n_send;
@@ -334,6 +343,123 @@ k_sparse_pull(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPullArgsN args)
   if (lb == 0 && tid == 0) *c.epoch = e0 + 2;
 }
 
+// Q0 of the push, fast path (pooled gradients, cvm_offset 2): the representative occurrence of every
+// unique key stores its record, straight into the owner's mailbox when the key occurs once in the
+// batch.  `s_bag`: this warp's shared-memory tile of 16 * PD floats.  Runs either inside k_sparse_push
+// (virtual-rank tests) or, in production, as its own launch k_push_records right before it: the
+// phase is a chain of dependent index / gradient loads per warp, and on its own it gets 64 warps per
+// SM to hide them instead of the 16 the optimizer phase of the cooperative kernel leaves.
+__device__ __forceinline__ void push_q0_direct(const PbxSparseDev& c, const PbxPushArgs& a, float* s_bag,
+                                               int64_t gtid, int64_t gstride, uint32_t tag) {
+  const int R = c.nranks;
+  const uint32_t cap = c.cap;
+  const int PD = c.push_stride;
+  const int pchunks = PD >> 2;
+  {
+    // A warp takes TB consecutive bags.  All keys of one bag push the SAME record (the bag's output
+    // gradient + the instance's show / click), so the warp first builds the TB bag records in shared
+    // memory with coalesced loads of the gradient rows, then hands them out: every lane owns one key
+    // occurrence (unique row and representative flag are coalesced loads, its bag is found by a
+    // shuffle search over the lod values the warp holds) and the records are copied ITEM-wise — item
+    // = (key, 16-byte chunk), adjacent lanes = adjacent chunks of one record — from shared memory to
+    // wherever the key's record lives.  No global load sits on the per-key path but two index loads.
+    const int hidden = 3 + c.table.L.embedx_dim;
+    const int lane = threadIdx.x & 31;
+    constexpr int TB = 16;                   // bags per warp task (several tasks per warp: even split)
+    const int64_t nbags = (int64_t)a.S * a.B;
+    const int64_t ntask = (nbags + TB - 1) / TB;
+    const int64_t wid = gtid >> 5, nw = gstride >> 5;
+    for (int64_t t = wid; t < ntask; t += nw) {
+      const int64_t g0 = t * TB;
+      const int32_t Lb = __ldg(a.lod + min(g0 + min(lane, TB), nbags));
+      const int32_t kb = __shfl_sync(0xffffffffu, Lb, 0);
+      const int32_t ke = __shfl_sync(0xffffffffu, Lb, TB);
+      if (ke <= kb) continue;
+      __syncwarp();
+      // (batches of 5 rounds: all gradient loads of a batch are issued before the first shared-memory
+      //  store waits for its value — a store right behind its load would serialise one L2 round trip
+      //  per round)
+      for (int base = 0; base < TB * PD; base += 32 * 5) {
+        float val[5];
+#pragma unroll
+        for (int u = 0; u < 5; ++u) {
+          const int idx = base + u * 32 + lane;
+          val[u] = 0.f;
+          if (idx >= TB * PD) continue;
+          const int l = idx / PD, w = idx - l * PD;
+          // (32-bit arithmetic on purpose: a 64-bit division by a runtime value is ~100 instructions, and
+          //  with one per element it, not memory, was what this phase cost)
+          const uint32_t gg = (uint32_t)min(g0 + l, nbags - 1);
+          const uint32_t s = gg / (uint32_t)a.B, b = gg - s * (uint32_t)a.B;
+          const int col = w - 1;             // push word w <-> value column w - 1, word 0 = slot id
+          if (col < 0) val[u] = (float)s;
+          else if (col >= hidden) val[u] = 0.f;
+          else if (col < 2) val[u] = __ldg(a.cvm + (int64_t)b * 2 + col);
+          else val[u] = a.grad_scale * __ldg(a.dout + (int64_t)b * a.ld_dout + (int64_t)s * a.Eo + (col - a.dim_off));
+        }
+#pragma unroll
+        for (int u = 0; u < 5; ++u) {
+          const int idx = base + u * 32 + lane;
+          if (idx < TB * PD) s_bag[idx] = val[u];
+        }
+      }
+      __syncwarp();
+      for (int32_t k0 = kb; k0 < ke; k0 += 32) {
+        const int32_t k = k0 + lane;
+        const bool valid = k < ke;
+        const int32_t kc = valid ? k : ke - 1;
+        const uint32_t uid = __ldg(a.restore + kc);
+        const bool rep = c.occ_rep[kc] != 0;
+        int lo = 0, hi = TB - 1;             // largest l with lod[g0 + l] <= k
+#pragma unroll
+        for (int step = 0; step < 4; ++step) {
+          const int mid = (lo + hi + 1) >> 1;
+          const int32_t Lm = __shfl_sync(0xffffffffu, Lb, mid);
+          if (Lm <= kc) lo = mid; else hi = mid - 1;
+        }
+        if (valid && !rep) {                 // merged in Q1 from the list
+          const uint32_t at = atomicAdd(c.send_cnt + 48, 1u);
+          c.dup_list[2 * (uint64_t)at] = (uint32_t)k;
+          c.dup_list[2 * (uint64_t)at + 1] = (uint32_t)(g0 + lo);
+        }
+        float* dstp = nullptr;               // destination of this lane's record (representatives only)
+        if (valid && rep) {
+          const uint32_t o = uid / cap;
+          if ((int)o == c.rank || R == 1 || c.uid_multi[uid] == tag) {
+            dstp = c.push_acc + (uint64_t)uid * PD;                  // local shard, or merged locally first
+          } else {
+            // the key occurs once in this batch: its record is final — it goes straight into the owner's
+            // mailbox over NVLink; the transfer hides behind this phase instead of being a phase of its own
+            dstp = c.push_mail[o] + ((uint64_t)c.rank * cap + (uid - o * cap)) * PD;
+          }
+        }
+        const unsigned long long dst64 = (unsigned long long)dstp;
+        const int nkeys = min(32, (int)(ke - k0));
+        const int items = nkeys * pchunks;
+        for (int i0 = 0; i0 < items; i0 += 32) {
+          const int i = i0 + lane;
+          const int q = i / pchunks;
+          const int r = min(q, 31), ch = i - q * pchunks;
+          const int lr = __shfl_sync(0xffffffffu, lo, r);
+          const unsigned long long dr = __shfl_sync(0xffffffffu, dst64, r);
+          if (i < items && dr != 0ull)
+            *reinterpret_cast<float4*>(reinterpret_cast<float*>(dr) + ch * 4) =
+                *reinterpret_cast<const float4*>(s_bag + lr * PD + ch * 4);
+        }
+      }
+    }
+  }
+}
+
+// stand-alone launch of the same phase (any grid; dynamic shared memory = warps per CTA * 16 * PD floats)
+__global__ void __launch_bounds__(256) k_push_records(const PbxSparseDev* __restrict__ ctx, PbxPushArgs a) {
+  extern __shared__ float4 s_rec[];
+  const PbxSparseDev& c = *ctx;
+  float* s_bag = reinterpret_cast<float*>(s_rec) + (size_t)(threadIdx.x >> 5) * 16 * c.push_stride;
+  push_q0_direct(c, a, s_bag, (int64_t)blockIdx.x * blockDim.x + threadIdx.x, (int64_t)gridDim.x * blockDim.x,
+                 (uint32_t)c.epoch[5]);
+}
+
 template <bool EMU>
 __global__ void __launch_bounds__(PBX_PUSH_THREADS, 1)
 k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args) {
@@ -356,29 +482,13 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
   // ---- Q0: initialise the merge rows in use.  Fast path (pooled gradients, cvm_offset 2): the
   // representative occurrence of every unique key STORES its record (no zero pass, no atomics);
   // other paths zero the rows and merge everything with atomics in Q1.
-  if (a.mode == 0 && a.cvm_offset == 2) {
-    const int hidden = 3 + c.table.L.embedx_dim;
-    const int64_t items = (int64_t)a.S * a.B * pchunks;
-    for (int64_t it = gtid; it < items; it += gstride) {
-      const int ch = (int)(it % pchunks);
-      const int64_t g = it / pchunks;
-      const int s = (int)(g / a.B);
-      const int b = (int)(g % a.B);
-      const int32_t k0 = __ldg(a.lod + g), k1 = __ldg(a.lod + g + 1);
-      if (k0 >= k1) continue;
-      float4 v;
-      float* vp = reinterpret_cast<float*>(&v);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const int col = ch * 4 + j - 1;  // push word w <-> value column w - 1
-        if (col < 0) vp[j] = (float)s;   // word 0 = slot id
-        else if (col >= hidden) vp[j] = 0.f;
-        else if (col < 2) vp[j] = __ldg(a.cvm + (int64_t)b * 2 + col);
-        else vp[j] = a.grad_scale * __ldg(a.dout + (int64_t)b * a.ld_dout + (int64_t)s * a.Eo + (col - a.dim_off));
-      }
-      for (int32_t k = k0; k < k1; ++k)
-        if (c.occ_rep[k])
-          *reinterpret_cast<float4*>(c.push_acc + (uint64_t)__ldg(a.restore + k) * PD + ch * 4) = v;
+  // fast path: pooled gradients, cvm_offset 2, and a shared-memory tile per warp that holds 16 bag records
+  const bool direct = a.mode == 0 && a.cvm_offset == 2 && c.q3_tile_rows > 0 && 16 * PD <= c.q3_warp_words;
+  const uint32_t tag = (uint32_t)c.epoch[5];               // tag of the pull this push belongs to
+  if (direct) {
+    if (!a.q0_done) {
+      extern __shared__ float4 s_q3[];
+      push_q0_direct(c, a, reinterpret_cast<float*>(s_q3) + (size_t)(tid >> 5) * c.q3_warp_words, gtid, gstride, tag);
     }
   } else {
     for (int o = 0; o < R; ++o) {
@@ -392,24 +502,20 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
   PBX_TS(9);
 
   // ---- Q1: merge by unique key (fused with the seqpool/CVM backward in mode 0)
-  if (a.mode == 0 && a.cvm_offset == 2) {
-    // One thread per (bag, 4-word chunk of the push record).  In CTR batches almost every unique
-    // key occurs once, so the merge is done in two passes instead of with one atomic per word:
-    //   pass A (before the grid barrier above... see Q0): every REPRESENTATIVE occurrence (the
-    //          first claimer of its key in the pull's dedup, c.occ_rep) STORES its record;
-    //   pass B (here): the few remaining occurrences are added with atomics / vector reductions.
+  if (direct) {
+    // In CTR batches almost every unique key occurs once, so the merge is two passes instead of one
+    // atomic per word: Q0 STORED the record of every representative occurrence (the first claimer of
+    // its key in the pull's dedup); here the few remaining occurrences, listed by Q0, are added with
+    // atomics / 16-byte vector reductions.
     // (reference: PushMergeCopy vs PushMergeCopyAtomic chosen by total < 2 * uniq, box_wrapper.cu:1034)
     const int hidden = 3 + c.table.L.embedx_dim;
-    const int64_t items = (int64_t)a.S * a.B * pchunks;
+    const uint32_t ndup = c.send_cnt[48];
+    const int64_t items = (int64_t)ndup * pchunks;
     for (int64_t it = gtid; it < items; it += gstride) {
       const int ch = (int)(it % pchunks);
-      const int64_t g = it / pchunks;
-      const int s = (int)(g / a.B);
-      const int b = (int)(g % a.B);
-      const int32_t k0 = __ldg(a.lod + g), k1 = __ldg(a.lod + g + 1);
-      bool any = false;
-      for (int32_t k = k0; k < k1; ++k) any |= (c.occ_rep[k] == 0);
-      if (!any) continue;
+      const int64_t e = it / pchunks;
+      const uint32_t k = c.dup_list[2 * e], g = c.dup_list[2 * e + 1];
+      const uint32_t s = g / (uint32_t)a.B, b = g - s * (uint32_t)a.B;
       float v[4];
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
@@ -418,16 +524,13 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
         else if (col < 2) v[j] = __ldg(a.cvm + (int64_t)b * 2 + col);
         else v[j] = a.grad_scale * __ldg(a.dout + (int64_t)b * a.ld_dout + (int64_t)s * a.Eo + (col - a.dim_off));
       }
-      for (int32_t k = k0; k < k1; ++k) {
-        if (c.occ_rep[k]) continue;
-        float* rec = c.push_acc + (uint64_t)__ldg(a.restore + k) * PD + ch * 4;
-        if (ch == 0) {
-          atomicAdd(rec + 1, v[1]);
-          atomicAdd(rec + 2, v[2]);
-          atomicAdd(rec + 3, v[3]);
-        } else {
-          pbx_red_add_v4(rec, v[0], v[1], v[2], v[3]);
-        }
+      float* rec = c.push_acc + (uint64_t)__ldg(a.restore + k) * PD + ch * 4;
+      if (ch == 0) {
+        atomicAdd(rec + 1, v[1]);
+        atomicAdd(rec + 2, v[2]);
+        atomicAdd(rec + 3, v[3]);
+      } else {
+        pbx_red_add_v4(rec, v[0], v[1], v[2], v[3]);
       }
     }
   } else if (a.mode == 0) {
@@ -482,6 +585,13 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
       float4* dst = reinterpret_cast<float4*>(c.push_mail[o] + (uint64_t)c.rank * cap * PD);  // remote
       // four independent 16-byte moves per thread in flight (local L2 read -> NVLink store)
       const int64_t step = (int64_t)nb * PBX_PUSH_THREADS;
+      if (direct) {
+        // only the records merged from several occurrences are still here; the others went out in Q0
+        const uint32_t* multi = c.uid_multi + (uint64_t)o * cap;
+        for (int64_t it = (int64_t)bl * PBX_PUSH_THREADS + tid; it < items; it += step)
+          if (multi[it / pchunks] == tag) dst[it] = __ldcg(src + it);
+        continue;
+      }
       for (int64_t it = (int64_t)bl * PBX_PUSH_THREADS + tid; it < items; it += 4 * step) {
         float4 v[4];
 #pragma unroll
@@ -496,6 +606,7 @@ k_sparse_push(const PbxSparseDev* __restrict__ ctxs, int nvr, PbxPushArgsN args)
   PBX_TSB(10);
   xbarrier<EMU>(grid, c, e0 + 1, lb == 0);
   PBX_TS(11);
+  if (lb == 0 && tid == 0) c.send_cnt[48] = 0;   // every CTA is past Q1: the duplicate list is consumed
 
   // ---- folded dense allreduce (one-shot per slice over peer memory, scale fused)
   if (a.dense_ctx) {
@@ -806,6 +917,9 @@ int pbx_sparse_create(void** out, void* table, int rank, int nranks, int64_t max
   PBX_CUDA_CHECK(cudaMemset(h.serve_cnt, 0, 64 * sizeof(uint32_t)));
   PBX_CUDA_CHECK(cudaMalloc(&h.mail_row, (size_t)nranks * cap * sizeof(uint32_t)));
   PBX_CUDA_CHECK(cudaMalloc(&h.push_acc, (size_t)nranks * cap * h.push_stride * sizeof(float)));
+  PBX_CUDA_CHECK(cudaMalloc(&h.dup_list, (size_t)max_keys * 2 * sizeof(uint32_t)));
+  PBX_CUDA_CHECK(cudaMalloc(&h.uid_multi, (size_t)nranks * cap * sizeof(uint32_t)));
+  PBX_CUDA_CHECK(cudaMemset(h.uid_multi, 0, (size_t)nranks * cap * sizeof(uint32_t)));
   PBX_CUDA_CHECK(cudaMalloc(&h.occ_rep, (size_t)max_keys + 16));
   PBX_CUDA_CHECK(cudaMemset(h.occ_rep, 0, (size_t)max_keys + 16));
   PBX_CUDA_CHECK(cudaMalloc(&h.epoch, 256));
@@ -857,6 +971,8 @@ int pbx_sparse_destroy(void* hnd) {
   cudaFree(c->h.mail_row);
   cudaFree(c->h.push_acc);
   cudaFree(c->h.occ_rep);
+  cudaFree(c->h.uid_multi);
+  cudaFree(c->h.dup_list);
   cudaFree(c->h.epoch);
   cudaFree(c->d);
   cudaFreeHost(c->status_host);
@@ -1078,6 +1194,21 @@ int pbx_sparse_push_dense(void* hnd, const uint32_t* d_restore, int64_t n, const
     args.a[0].dense_scale = dense_scale;
   }
   const PbxSparseDev* dctx = c->d;
+  const int PDh = c->h.push_stride;
+  if (mode == 0 && cvm_offset == 2 && c->h.q3_tile_rows > 0 && 16 * PDh <= c->h.q3_warp_words &&
+      (int64_t)S * B < 0x7fffffffll && S * B > 0) {
+    const size_t smem = (size_t)(256 / 32) * 16 * PDh * sizeof(float);
+    if (smem <= 48 * 1024) {
+      const int64_t ntask = ((int64_t)S * B + 15) / 16;
+      int grid = (int)((ntask + 7) / 8);
+      const int cap_grid = pbx_num_sms() * 8;
+      if (grid > cap_grid) grid = cap_grid;
+      k_push_records<<<grid, 256, smem, st>>>(dctx, args.a[0]);
+      PBX_CUDA_CHECK(cudaGetLastError());
+      pbx_note_launch(1);
+      args.a[0].q0_done = 1;
+    }
+  }
   int nvr = 1;
   void* kargs[] = {(void*)&dctx, (void*)&nvr, (void*)&args};
   PBX_CUDA_CHECK(cudaLaunchCooperativeKernel((void*)k_sparse_push<false>, dim3(c->grid_blocks),

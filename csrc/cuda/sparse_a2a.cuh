@@ -24,6 +24,8 @@ struct PbxSparseDev {
   uint32_t* serve_cnt;  // [nranks] keys served for each requester in the last pull
   uint32_t* mail_row;   // [nranks*cap] table row of every served key (reused by push)
   float* push_acc;      // [nranks*cap*push_stride] local merge buffer
+  uint32_t* uid_multi;  // [nranks*cap] == tag of the last pull (epoch[5]) when the unique key occurred more than once in it
+  uint32_t* dup_list;   // [2*max_keys] (occurrence, bag) of the non-representative occurrences of the current push
   uint8_t* occ_rep;     // [max_keys] 1 = this occurrence is the representative (first claimer) of its unique key in the last pull
   uint64_t* epoch;      // barrier epoch counter
   int* status;          // 0 ok, 1 mailbox overflow, 2 barrier timeout

@@ -149,7 +149,7 @@ class SparseEngine:
 
     PULL_PHASES = ("P0 reset", "P1 dedup+route keys", "P2 restore idx", "P2 clear dedup + barrier",
                    "P3 serve rows + barrier")
-    PUSH_PHASES = ("Q0 zero merge rows", "Q1 merge (seqpool bwd)", "Q2 ship + barrier", "Q3 optimizer")
+    PUSH_PHASES = ("Q0 init (records go out in k_push_records before this kernel)", "Q1 merge duplicate keys", "Q2 ship + barrier", "Q3 optimizer")
 
     def phase_times(self) -> dict:
         """Wall time (us) of every phase of the last pull and the last push on this rank, from
