@@ -140,6 +140,7 @@ class Worker:
         self.loss = torch.zeros((), device=self.dev)
         self.graph_fb = None
         self.graph_opt = None
+        self.nccl_barrier = None            # threading.Barrier shared by the workers (set by run())
         self.flush_buf = torch.empty(256 << 20, dtype=torch.uint8, device=self.dev)
 
     # -- dense part: CVM transform + DeepFM (FM + deep tower) + log loss + backward ------------
@@ -233,9 +234,17 @@ class Worker:
         if lib.ref_push_sparse(h, d, gp, sl, S, E, B) != 0:
             raise RuntimeError(lib.ref_last_error().decode())
         if self.ndev > 1:
+            # All workers meet before and after the allreduce (the reference has the same device for its own
+            # runs, FLAGS_enable_dense_nccl_barrier).  Without it a worker that is still inside HeterComm can
+            # reach a cudaMalloc (allocator miss on a new batch length) on a device whose NCCL kernel is
+            # already spinning for that very worker's contribution — the classic implicit-sync deadlock,
+            # which is what an 8-GPU run of this arm ran into.
+            self.nccl_barrier.wait(timeout=120)
             if lib.ref_allreduce_sum(h, d, C.c_void_p(self.flat_g.data_ptr()), C.c_int64(self.flat_g.numel()),
                                      C.c_void_p(self.stream.cuda_stream)) != 0:
                 raise RuntimeError(lib.ref_last_error().decode())
+            self.stream.synchronize()
+            self.nccl_barrier.wait(timeout=120)
         self.graph_opt.replay()
         return self.loss
 
@@ -287,8 +296,22 @@ def run(args) -> int:
     if ndev > 1 and lib.ref_nccl_init(h) != 0:
         return unavailable("ncclCommInitAll failed: " + lib.ref_last_error().decode()[:200])
 
+    # watchdog: a run that does not finish in time reports itself unavailable instead of hanging the caller
+    deadline_s = float(os.environ.get("PBX_REF_DEADLINE_S", 120 + 15 * ndev))
+    finished = threading.Event()
+
+    def watchdog():
+        if not finished.wait(deadline_s):
+            print(json.dumps({"impl": "reference", "n_gpus": ndev,
+                              "unavailable": f"reference arm did not finish within {int(deadline_s)} s at {ndev} GPUs "
+                                             "(HeterComm worker threads stalled)"}), flush=True)
+            os._exit(0)
+    threading.Thread(target=watchdog, daemon=True).start()
+
     workers = [Worker(d, args, lib, h, ndev, hidden) for d in range(ndev)]
+    nccl_barrier = threading.Barrier(ndev)
     for w in workers:
+        w.nccl_barrier = nccl_barrier
         w.capture()
     host_batches = [make_host_batches(args, d, ndev, args.n_batches) for d in range(ndev)]
     barrier = threading.Barrier(ndev)
@@ -361,9 +384,14 @@ def run(args) -> int:
             barrier.wait()
             results[d] = (dev_ms, ea.elapsed_time(eb), loss_val, h2d // args.steps, d2h // args.steps)
         except Exception as e:  # noqa: BLE001
+            # the other workers are (or will be) waiting for this one inside NCCL or at a barrier: there is no
+            # clean way to unwind them, so report and leave
             import traceback
-            errors.append(f"worker {d}: {e}\n{traceback.format_exc()}")
-            barrier.abort()
+            print(f"worker {d}: {e}\n{traceback.format_exc()}", file=sys.stderr, flush=True)
+            print(json.dumps({"impl": "reference", "n_gpus": ndev,
+                              "unavailable": f"reference arm failed at run time on worker {d}: {str(e)[:160]}"}),
+                  flush=True)
+            os._exit(0)
 
     stop = threading.Event()
     ct = threading.Thread(target=clocks_thread, args=(stop,), daemon=True)
@@ -375,6 +403,7 @@ def run(args) -> int:
     for t in threads:
         t.join()
     wall = time.time() - wall0
+    finished.set()
     stop.set()
     ct.join(timeout=2)
     if errors:
