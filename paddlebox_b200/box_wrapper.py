@@ -162,6 +162,7 @@ class BoxWrapper:
             from .ops.sparse_table import SparseTable
             from .parallel.sparse_engine import SparseEngine
             cap = int(table_capacity or (1 << 22))
+            self._pass_builder = None
             self.table = SparseTable(cap, self.embedx_dim, self.optimizer, self.config, seed=self.rank,
                                      device=self.device.index)
             cap_pair = 0
@@ -233,19 +234,25 @@ class BoxWrapper:
         keys = self._pass_keys if self._pass_keys is not None else np.zeros(0, np.uint64)
         if self.use_cuda:
             self.table.clear()
-            # chunked H2D so that staging memory stays bounded (heter_comm_inl.h:671-731)
-            chunk = 1 << 20
-            for i in range(0, keys.size, chunk):
-                ks = keys[i:i + chunk]
-                rows = self.host_table.fetch_rows(ks, create=True)
-                dk = torch.from_numpy(ks.view(np.int64)).to(self.device, non_blocking=False)
-                dr = torch.from_numpy(rows).to(self.device, non_blocking=False)
-                self.table.insert(dk, dr)
+            # streamed build (pass_build.py): host fetch of chunk k+1 into a pinned slot overlaps the H2D copy
+            # and the insert kernel of chunk k; staging memory is a fixed pool reused by every pass
+            # (ps_gpu_wrapper.cc:684-955, heter_comm_inl.h:671-731, mem_pool.h:28-102)
+            self.last_pass_build = self.pass_builder().build(keys) if keys.size else {}
         else:
             if keys.size:
                 self.host_table.fetch_rows(keys, create=True)  # create missing rows
         self._in_pass = True
         self.timers.add("begin_pass", time.time() - t0)
+
+    def pass_builder(self):
+        """The pass build / write-back pipeline of this shard (created on first use, staging pool reused)."""
+        pb = getattr(self, "_pass_builder", None)
+        if pb is None:
+            from .pass_build import PassBuilder
+            pb = self._pass_builder = PassBuilder(self.host_table, self.table.insert, self.host_table.layout.stride,
+                                                  self.device, chunk=int(FLAGS.pbx_pass_chunk_rows),
+                                                  depth=3, fetch_threads=int(FLAGS.pbx_pass_fetch_threads))
+        return pb
 
     def end_pass(self, need_save_delta: bool = False, delta_path: str = "") -> None:
         """Write the HBM working set back to the host tier (``EndPass``)."""
@@ -255,7 +262,8 @@ class BoxWrapper:
             self.engine.check_status()
             dk, dr = self.table.dump(only_dirty=True, clear_dirty=True)
             if dk.numel():
-                self.host_table.store_rows(dk.cpu().numpy().view(np.uint64), dr.cpu().numpy(), mark_dirty=True)
+                # bounded pinned chunks: D2H of chunk k+1 overlaps the host-table store of chunk k
+                self.last_pass_write_back = self.pass_builder().write_back(dk, dr, mark_dirty=True)
         self._in_pass = False
         if need_save_delta and delta_path:
             self.save_delta(delta_path)
@@ -302,7 +310,8 @@ class BoxWrapper:
             torch.cuda.synchronize(self.device)
             dk, dr = self.table.dump(only_dirty=True, clear_dirty=True)
             if dk.numel():
-                self.host_table.store_rows(dk.cpu().numpy().view(np.uint64), dr.cpu().numpy(), mark_dirty=True)
+                # bounded pinned chunks: D2H of chunk k+1 overlaps the host-table store of chunk k
+                self.last_pass_write_back = self.pass_builder().write_back(dk, dr, mark_dirty=True)
 
     def save_base(self, batch_model_path: str, xbox_model_path: str = "", date: str = "") -> str:
         """Full training checkpoint ("batch model", every optimizer state) + serving base
@@ -511,6 +520,7 @@ class BoxWrapper:
         self.engine = None
         self.router = None
         self.table = None
+        self._pass_builder = None
         self.host_table = None
         self._metrics.clear()
         self._initialized = False

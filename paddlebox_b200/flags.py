@@ -91,6 +91,8 @@ _d("enable_debug_print_metrics_info", False, "verbose AUC computation (metrics.c
 _d("pbx_use_cuda_graph", True, "capture the training step in a CUDA graph when shapes allow")
 _d("pbx_pack_threads", 4, "background threads packing mini-batches into staging buffers (per loader)")
 _d("pbx_overlap_wgrad", False, "weight-gradient GEMMs on a side stream, concurrently with the dgrad chain (measured: no gain over the grouped launch)")
+_d("pbx_pass_chunk_rows", 1 << 19, "rows per staging slot of the pass build / write-back pipeline (3 pinned slots)")
+_d("pbx_pass_fetch_threads", 4, "CPU threads fetching host-table rows into pinned staging slots during begin_pass")
 _d("pbx_fold_dense_allreduce", True, "data-parallel dense-gradient allreduce rides on the sparse push kernel's barriers")
 _d("pbx_sparse_dist", False, "GPU worlds: route pull/push through torch.distributed all-to-all (multi-node) instead of the one-node peer-memory engine; CPU worlds with > 1 rank always route this way")
 _d("pbx_sparse_cap_factor", 2.0, "mailbox capacity = factor * max_keys / nranks")

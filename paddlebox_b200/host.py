@@ -81,6 +81,13 @@ class HostTable:
         N.hcheck(N.host().pbh_table_fetch_rows(self._h, _u64p(k), C.c_int64(k.size), _f32p(out), int(create)))
         return out
 
+    def fetch_rows_into(self, keys, out: np.ndarray, create: bool = True) -> None:
+        """``fetch_rows`` straight into a caller-owned buffer (a pinned staging slot of the pass builder):
+        no intermediate array, and the native call runs without the GIL, so several threads fetch at once."""
+        k = _as_np_u64(keys)
+        assert out.dtype == np.float32 and out.flags["C_CONTIGUOUS"] and out.shape == (k.size, self.layout.stride)
+        N.hcheck(N.host().pbh_table_fetch_rows(self._h, _u64p(k), C.c_int64(k.size), _f32p(out), int(create)))
+
     def store_rows(self, keys, rows, mark_dirty: bool = True) -> None:
         k = _as_np_u64(keys)
         r = np.ascontiguousarray(rows.detach().cpu().numpy() if isinstance(rows, torch.Tensor) else rows,
