@@ -1,30 +1,168 @@
-"""HeterPS-flavoured names over the same engine.
+"""The open twin of the PS front end: ``PSGPUWrapper`` with its pass-build pipeline.
 
 The reference ships two front ends for the GPU parameter server: the closed-library
-``BoxWrapper`` and its open twin ``PSGPUWrapper`` / ``pull_gpups_sparse`` / ``PSGPUTrainer``
+``BoxWrapper`` and ``PSGPUWrapper`` / ``pull_gpups_sparse`` / ``PSGPUTrainer``
 (fleet/ps_gpu_wrapper.h:1-728, operators/pull_gpups_sparse_op.h, ps_gpu_trainer.cc:37-420).
-Both drive one sharded HBM table here, so the twin is a naming layer.
+Both drive the same sharded HBM table and sparse engine here; what ``PSGPUWrapper`` adds is its own pass
+lifecycle — a background build thread fed through three channels
+(``data_ready -> buildcpu_ready -> gpu_free``, fleet/ps_gpu_wrapper.cc:885-955):
+
+    load_into_memory(dataset)      dataset loaded, a ``HeterContext`` is queued            (:885-900)
+      pre-build thread             PreBuildTask: the pass's unique keys, sharded by owner   (:114-335)
+                                   BuildPull: the rows of those keys fetched / created in
+                                   the CPU table, into the task's host pool                 (:337-682)
+    begin_pass()                   waits for the built task AND for the GPU to be free
+                                   (previous pass ended), then BuildGPUTask: host pool ->
+                                   HBM, streamed                                             (:684-883, :957-981)
+    end_pass()                     HBM -> CPU table, GPU handed back                        (:983-1079)
+
+so the CPU half of pass N+1 (key collection, CPU-table fetch) overlaps the training of pass N.
 """
 from __future__ import annotations
+
+import queue
+import threading
+import time
+
+import numpy as np
 
 from .box_wrapper import BoxWrapper
 from .ops.pull_box_sparse import pull_box_sparse, sparse_embedding_pool
 from .trainer import CTRTrainer, Executor, TrainerConfig
 
 
+class HeterContext:
+    """One pass's build task (reference fleet/heter_context.h:41-250): the dataset it belongs to, the unique
+    keys this rank owns, the rows staged for them on the host, and the time every stage took."""
+
+    def __init__(self, dataset=None, keys=None, date: str | None = None):
+        self.dataset, self.date = dataset, date
+        self.raw_keys = keys                  # explicit key list (tests / custom feeds) instead of a dataset
+        self.keys: np.ndarray | None = None   # PreBuildTask result: unique, owned by this rank, sorted
+        self.rows: np.ndarray | None = None   # BuildPull result: [n, stride] host pool of the pass
+        self.timing: dict = {}
+        self.error: BaseException | None = None
+
+
 class PSGPUWrapper(BoxWrapper):
-    """``PSGPUWrapper.get_instance()`` — same object model as :class:`BoxWrapper`."""
+    """``PSGPUWrapper.get_instance()`` — the object model of :class:`BoxWrapper` plus the HeterPS pass
+    pipeline described in the module docstring."""
 
-    # PreBuildTask + BuildPull + BuildGPUTask == begin/end feed pass + begin pass
-    def build_task(self, keys=None) -> None:
-        self.begin_feed_pass()
-        if keys is not None:
-            self.feed_pass(keys)
-        self.end_feed_pass()
-        self.begin_pass()
+    # ---- channels and the build thread (start_build_thread, ps_gpu_wrapper.cc:885-955) -----------------
+    def start_build_thread(self) -> None:
+        if getattr(self, "_build_thread", None) is not None:
+            return
+        self._data_ready: "queue.Queue" = queue.Queue(maxsize=3)
+        self._buildcpu_ready: "queue.Queue" = queue.Queue(maxsize=3)
+        self._gpu_free: "queue.Queue" = queue.Queue(maxsize=1)
+        self._gpu_free.put(None)              # the GPU starts out free
+        self.current_task: HeterContext | None = None
+        self._running = True
+        self._build_thread = threading.Thread(target=self._pre_build_loop, name="psgpu-pre-build", daemon=True)
+        self._build_thread.start()
 
-    def load_into_memory(self, dataset) -> None:
+    def _pre_build_loop(self) -> None:
+        while True:
+            task = self._data_ready.get()
+            if task is None:
+                return
+            try:
+                self.pre_build_task(task)
+                self.build_pull(task)
+            except BaseException as e:  # noqa: BLE001  (handed to begin_pass, which raises it)
+                task.error = e
+            self._buildcpu_ready.put(task)
+
+    def stop_build_thread(self) -> None:
+        if getattr(self, "_build_thread", None) is not None:
+            self._data_ready.put(None)
+            self._build_thread.join(timeout=30)
+            self._build_thread = None
+
+    # ---- the three build stages ---------------------------------------------------------------------------
+    def pre_build_task(self, task: HeterContext) -> None:
+        """PreBuildTask: the unique keys of the pass, each routed to the rank that owns its shard."""
+        t0 = time.time()
+        from .host import partition_by_owner, sort_unique_u64
+        raw = task.raw_keys if task.raw_keys is not None else task.dataset.unique_keys()
+        raw = np.ascontiguousarray(raw.cpu().numpy() if hasattr(raw, "cpu") else raw)
+        if raw.dtype.kind not in "iu" or raw.dtype.itemsize != 8:
+            raise TypeError(f"pass keys must be 64-bit integers, got {raw.dtype}")
+        raw = (raw.view(np.uint64) if raw.dtype != np.uint64 else raw).reshape(-1)
+        keys = sort_unique_u64(np.concatenate([np.zeros(1, np.uint64), raw]))       # key 0 is always registered
+        if self.world_size > 1:
+            from .parallel.cluster import Cluster
+            mine = Cluster(self.group).all_to_all_arrays(partition_by_owner(keys, self.world_size))
+            keys = sort_unique_u64(np.concatenate(mine)) if mine else np.zeros(0, np.uint64)
+        task.keys = keys
+        task.timing["pre_build_s"] = time.time() - t0
+
+    def build_pull(self, task: HeterContext) -> None:
+        """BuildPull: fetch (or create) the rows of the pass's keys in the CPU table into the task's host pool."""
+        t0 = time.time()
+        task.rows = self.host_table.fetch_rows(task.keys, create=True) if task.keys.size else \
+            np.zeros((0, self.host_table.layout.stride), np.float32)
+        task.timing["build_pull_s"] = time.time() - t0
+
+    def build_gpu_task(self, task: HeterContext) -> None:
+        """BuildGPUTask: the task's host pool -> this rank's HBM shard (streamed through the staging pool)."""
+        t0 = time.time()
+        if self.use_cuda:
+            self.table.clear()
+            if task.keys.size:
+                pool = _PrefetchedRows(task.keys, task.rows, self.host_table)
+                from .pass_build import PassBuilder
+                pb = PassBuilder(pool, self.table.insert, self.host_table.layout.stride, self.device,
+                                 chunk=min(int(1 << 19), max(int(task.keys.size), 1)), depth=2, fetch_threads=1)
+                task.timing["gpu_build"] = pb.build(task.keys)
+        self._pass_keys = task.keys
+        self._in_pass = True
+        task.timing["build_gpu_s"] = time.time() - t0
+
+    # ---- the reference's entry points ------------------------------------------------------------------------
+    def load_into_memory(self, dataset, date: str | None = None) -> HeterContext:
+        """``LoadIntoMemory``: load the dataset, then queue its build task for the pre-build thread."""
+        self.start_build_thread()
+        if date:
+            self.set_date(date)
         dataset.load_into_memory()
+        task = HeterContext(dataset=dataset, date=date)
+        self._data_ready.put(task)
+        return task
+
+    def build_task(self, keys=None) -> HeterContext:
+        """Queue a build task for an explicit key list (no dataset) and start the pass."""
+        self.start_build_thread()
+        task = HeterContext(keys=np.zeros(0, np.uint64) if keys is None else keys)
+        self._data_ready.put(task)
+        self.begin_pass()
+        return task
+
+    def begin_pass(self) -> None:
+        """``BeginPass``: take the next built task, wait until the GPU is free, build the HBM table."""
+        if getattr(self, "_build_thread", None) is None:         # used as a plain BoxWrapper
+            return super().begin_pass()
+        assert self._initialized, "call init_gpu_ps / initialize_gpu_and_load_model first"
+        t0 = time.time()
+        task = self._buildcpu_ready.get()
+        if task.error is not None:
+            raise task.error
+        self._gpu_free.get()                                     # previous pass must have ended
+        self.build_gpu_task(task)
+        self.current_task = task
+        self.timers.add("begin_pass", time.time() - t0)
+
+    def end_pass(self, need_save_delta: bool = False, delta_path: str = "") -> None:
+        """``EndPass``: HBM -> CPU table, then the GPU is free for the next built task."""
+        had_task = getattr(self, "current_task", None) is not None
+        super().end_pass(need_save_delta, delta_path)
+        if had_task:
+            self.current_task = None
+            self._gpu_free.put(None)
+
+    def finalize(self) -> None:
+        self.stop_build_thread()
+        super().finalize()
 
     def set_slot_vector(self, slots) -> None:
         self.slot_vector = list(slots)
@@ -121,12 +259,65 @@ class PSGPUWrapper(BoxWrapper):
         self.initialize_gpu_and_load_model(conf or {}, **kw)
 
 
+class _PrefetchedRows:
+    """Host-table face of a task's already fetched pool (BuildPull ran in the background): chunk lookups
+    are slices of the pool, writes go to the real host table."""
+
+    def __init__(self, keys: np.ndarray, rows: np.ndarray, host_table):
+        self.keys, self.rows, self.host_table = keys, rows, host_table
+        self.layout = host_table.layout
+
+    def fetch_rows_into(self, keys: np.ndarray, out: np.ndarray, create: bool = True) -> None:
+        i0 = int(np.searchsorted(self.keys, keys[0])) if keys.size else 0
+        out[:] = self.rows[i0:i0 + keys.size]                   # chunks are contiguous runs of the sorted key list
+
+    def store_rows(self, keys, rows, mark_dirty=True):
+        self.host_table.store_rows(keys, rows, mark_dirty=mark_dirty)
+
+
 def pull_gpups_sparse(batch, size=None, offset: int = 0, box=None):
     """``_pull_gpups_sparse`` (python/paddle/fluid/layers/nn.py): HeterPS twin of ``pull_box_sparse``."""
     return pull_box_sparse(batch, size=size, offset=offset, box=box)
 
 
-PSGPUTrainer = CTRTrainer
-PSGPUWorker = CTRTrainer
+class PSGPUWorker(CTRTrainer):
+    """Per-GPU worker of the HeterPS flavour (ps_gpu_worker.cc:36-310): ``TrainFiles`` = one pass over the
+    batches the dataset dealt to this worker, on the sparse table the wrapper built for the pass."""
+
+    def train_files(self, dataset, **kw) -> dict:
+        return self.train_from_dataset(dataset, **kw)
+
+
+class PSGPUTrainer:
+    """``PSGPUTrainer`` (ps_gpu_trainer.cc:37-420): ``Initialize`` configures the GPU server from the fleet
+    desc (``InitializeGPUServer`` :137-254), ``Run`` trains one pass through the wrapper's pipeline
+    (``BeginPass -> TrainFiles -> EndPass``), ``Finalize`` merges the dense parameters back
+    (``MergeDenseParam`` :359-369 — with one process per GPU every rank already holds the synchronised
+    dense parameters, so this returns them)."""
+
+    def __init__(self, model, wrapper: PSGPUWrapper | None = None, config: TrainerConfig | None = None,
+                 sparse_conf: dict | None = None, **init_kw):
+        self.wrapper = wrapper or PSGPUWrapper.get_instance()
+        if not self.wrapper._initialized:
+            self.wrapper.init_gpu_server(sparse_conf or {}, **init_kw)
+        self.worker = PSGPUWorker(model, self.wrapper, config or TrainerConfig())
+
+    def run(self, dataset, date: str | None = None, need_save_delta: bool = False, delta_path: str = "") -> dict:
+        self.wrapper.load_into_memory(dataset, date)
+        self.wrapper.begin_pass()
+        try:
+            stats = self.worker.train_files(dataset)
+        finally:
+            self.wrapper.end_pass(need_save_delta, delta_path)
+        stats["build"] = dict(self.wrapper.timers.summary()) if hasattr(self.wrapper.timers, "summary") else {}
+        return stats
+
+    def finalize(self) -> dict:
+        self.worker.finalize()
+        named = self.worker.model.named_dense_params() if hasattr(self.worker.model, "named_dense_params") \
+            else self.worker.model.named_parameters()
+        return {n: p.detach().cpu() for n, p in named}
+
+
 __all__ = ["PSGPUWrapper", "pull_gpups_sparse", "PSGPUTrainer", "PSGPUWorker", "sparse_embedding_pool", "Executor",
            "TrainerConfig"]

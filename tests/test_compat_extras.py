@@ -133,7 +133,7 @@ def test_store_q_value_and_gpups_names(box):
     host = F.store_q_value(q, batch=b, device_id=0)
     assert len(host) == 2 and torch.equal(b.q_values[1], q[1]) and F.stored_q_values(0) is host
     assert ps_gpu.PSGPUWrapper.get_instance() is box          # one PS per process
-    assert ps_gpu.PSGPUTrainer is CTRTrainer and callable(ps_gpu.pull_gpups_sparse)
+    assert issubclass(ps_gpu.PSGPUWorker, CTRTrainer) and callable(ps_gpu.pull_gpups_sparse)
 
 
 def test_merge_multi_models(tmp_path, box):
@@ -457,5 +457,60 @@ def test_psgpu_wrapper_pybind_names(tmp_path):
         ps.build_task(torch.arange(1, 20))
         assert ps.host_table.size() == 20
         ps.end_pass()
+    finally:
+        BoxWrapper.reset_instance()
+
+
+def test_psgpu_pass_pipeline_overlaps_build_with_training(tmp_path):
+    """data_ready -> buildcpu_ready -> gpu_free (ps_gpu_wrapper.cc:885-955): the CPU half of pass 2 is built while
+    pass 1 is still "training"; begin_pass of pass 2 waits for end_pass of pass 1; errors of the build thread
+    surface in begin_pass; PSGPUTrainer.run drives a dataset through the same pipeline."""
+    import threading
+    import time
+    import torch
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    from paddlebox_b200.dataset import DatasetFactory
+    from paddlebox_b200.models.ctr import CtrDnn
+    from paddlebox_b200.ps_gpu import HeterContext, PSGPUTrainer, PSGPUWrapper
+    from tests.util_data import slot_vars, write_files
+    BoxWrapper.reset_instance()
+    ps = PSGPUWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=0, world_size=1)
+    try:
+        ps.init_gpu_ps([0], {"mf_create_thresholds": 0.0})
+        ps.start_build_thread()
+        t1, t2 = HeterContext(keys=np.arange(1, 101, dtype=np.uint64)), HeterContext(keys=np.arange(50, 301, dtype=np.uint64))
+        ps._data_ready.put(t1)
+        ps._data_ready.put(t2)                            # queued while pass 1 has not even begun
+        ps.begin_pass()
+        assert ps.current_task is t1 and np.array_equal(ps._pass_keys, np.arange(0, 101, dtype=np.uint64))
+        deadline = time.time() + 10
+        while t2.rows is None and time.time() < deadline:  # pass 2's CPU build finishes during pass 1
+            time.sleep(0.01)
+        assert t2.rows is not None and t2.rows.shape == (252, ps.host_table.layout.stride)
+        assert ps.host_table.size() == 301                  # keys 0..300 exist in the CPU table already
+        started = []
+        th = threading.Thread(target=lambda: (ps.begin_pass(), started.append(time.time())))
+        th.start()
+        time.sleep(0.3)
+        assert not started                                  # the GPU is still owned by pass 1
+        t_end = time.time()
+        ps.end_pass()
+        th.join(timeout=10)
+        assert started and started[0] >= t_end and ps.current_task is t2
+        assert {"pre_build_s", "build_pull_s", "build_gpu_s"} <= set(t2.timing)
+        ps.end_pass()
+        bad = HeterContext(keys="not keys")
+        ps._data_ready.put(bad)
+        with pytest.raises(Exception):
+            ps.begin_pass()
+        # a dataset through PSGPUTrainer.run
+        ds = DatasetFactory().create_dataset("InMemoryDataset")
+        ds.set_use_var(slot_vars(3, 2)); ds.set_batch_size(16); ds.set_thread(1)
+        ds.set_filelist(write_files(str(tmp_path), n_files=1, lines_per_file=64, n_sparse=3, n_dense=2, key_space=30))
+        torch.manual_seed(0)
+        tr = PSGPUTrainer(CtrDnn(num_slots=3, embedx_dim=4, dense_dim=2, hidden=(8,)), ps)
+        stats = tr.run(ds)
+        assert stats["instances"] == 64 and ps.current_task is None
+        assert "fc_0.w_0" in tr.finalize()
     finally:
         BoxWrapper.reset_instance()
