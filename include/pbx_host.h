@@ -122,6 +122,36 @@ int pbh_graph_sample_neighbors(void* g, int type, const uint64_t* nodes, int64_t
 int pbh_graph_random_walk(void* g, const int* metapath, int n_meta, const uint64_t* starts, int64_t n,
                           int walk_len, uint64_t seed, uint64_t* out, int32_t* out_len);
 
+/* weighted edges (load_edge_file with a weight column; weighted neighbour sample of graph_gpu_ps_table_inl.cu) */
+int pbh_graph_add_edges_weighted(void* g, int type, const uint64_t* src, const uint64_t* dst, const float* w,
+                                 int64_t n, int reverse);
+int pbh_graph_load_weighted_edge_file(void* g, int type, const char* path, int reverse, int64_t* n_loaded);
+int pbh_graph_is_weighted(void* g, int type);
+int pbh_graph_export_weights(void* g, int type, float* out);
+int pbh_graph_sample_neighbors_weighted(void* g, int type, const uint64_t* nodes, int64_t n, int k, uint64_t seed,
+                                        uint64_t* out, int32_t* out_cnt);
+/* node types with feature slots (load_node_file / get_feature_of_nodes / get_all_feature_ids / load_node_weight,
+ * heter_ps/graph_gpu_wrapper.h:50-99) */
+int pbh_graph_add_nodes(void* g, int ntype, const uint64_t* ids, int64_t n, const int64_t* offsets,
+                        const int32_t* slots, const uint64_t* values);
+int pbh_graph_load_node_file(void* g, int ntype, const char* path, const char* type_name, char sep, int64_t* n_loaded);
+int64_t pbh_graph_num_typed_nodes(void* g, int ntype);
+int pbh_graph_export_typed_nodes(void* g, int ntype, uint64_t* out);
+int pbh_graph_node_features(void* g, int ntype, const uint64_t* nodes, int64_t n, const int32_t* slot_ids, int n_slots,
+                            uint64_t* out);
+int pbh_graph_all_feature_ids(void* g, int ntype, uint64_t* out, int64_t* n_out);
+int pbh_graph_load_node_weight(void* g, int ntype, const char* path, int64_t* n_set);
+int pbh_graph_node_weights(void* g, int ntype, const uint64_t* nodes, int64_t n, float* out);
+/* partitions for paging a graph larger than HBM (make_partitions / get_partition_num / load_next_partition /
+ * get_partition / export_partition_files, graph_gpu_wrapper.h:57-62) */
+int pbh_graph_make_partitions(void* g, int type, int64_t byte_size, int device_len, int* n_parts);
+int pbh_graph_partition_num(void* g, int type);
+int pbh_graph_next_partition(void* g, int type);
+int pbh_graph_partition_shape(void* g, int type, int part, int64_t* n_nodes, int64_t* n_edges);
+int pbh_graph_export_partition(void* g, int type, int part, uint64_t* node_ids, int64_t* row_ptr, uint64_t* col_ids,
+                               float* weights);
+int pbh_graph_export_partition_files(void* g, int type, const char* dir);
+
 /* InputTable key index: string key -> row offset, 0 = miss (InputTable::AddIndexData / GetIndexOffset,
  * fleet/box_wrapper.h:124-197).  Attached to a dataset, a parser plugin that also exports
  *   void pbx_set_offset_func(uint64_t (*fn)(void* user, const char* key, size_t len), void* user)

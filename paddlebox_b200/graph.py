@@ -109,6 +109,128 @@ class GraphTable:
         n_types = N.host().pbh_graph_num_types(self._h)
         return DeviceGraph({t: self.csr(t) for t in (etypes if etypes is not None else range(n_types))}, device)
 
+    # ---- weighted edges ------------------------------------------------------------------------------
+    def add_weighted_edges(self, src, dst, weight, etype: int = 0, reverse: bool = False) -> None:
+        s = np.ascontiguousarray(src, dtype=np.uint64)
+        d = np.ascontiguousarray(dst, dtype=np.uint64)
+        w = np.ascontiguousarray(weight, dtype=np.float32)
+        assert s.shape == d.shape == w.shape
+        N.hcheck(N.host().pbh_graph_add_edges_weighted(self._h, etype, _u64p(s), _u64p(d),
+                                                       w.ctypes.data_as(C.POINTER(C.c_float)), C.c_int64(s.size),
+                                                       int(reverse)))
+
+    def load_weighted_edge_file(self, path: str, etype: int = 0, reverse: bool = False) -> int:
+        """Text file ``src<TAB>dst<TAB>weight`` per line (a missing weight counts as 1)."""
+        n = C.c_int64()
+        N.hcheck(N.host().pbh_graph_load_weighted_edge_file(self._h, etype, path.encode(), int(reverse), C.byref(n)))
+        return n.value
+
+    def is_weighted(self, etype: int = 0) -> bool:
+        return bool(N.host().pbh_graph_is_weighted(self._h, etype))
+
+    def edge_weights(self, etype: int = 0) -> np.ndarray:
+        """Weight of every CSR edge, aligned with ``csr(etype)[2]``."""
+        w = np.empty(self.num_edges(etype), np.float32)
+        N.hcheck(N.host().pbh_graph_export_weights(self._h, etype, w.ctypes.data_as(C.POINTER(C.c_float))))
+        return w
+
+    def sample_neighbors_weighted(self, nodes, k: int, etype: int = 0, seed: int = 0):
+        """Like ``sample_neighbors`` with probability proportional to the edge weight (without replacement)."""
+        q = np.ascontiguousarray(nodes, dtype=np.uint64)
+        out = np.empty((q.size, k), np.uint64)
+        cnt = np.empty(q.size, np.int32)
+        N.hcheck(N.host().pbh_graph_sample_neighbors_weighted(self._h, etype, _u64p(q), C.c_int64(q.size), k,
+                                                              C.c_uint64(seed), _u64p(out),
+                                                              cnt.ctypes.data_as(C.POINTER(C.c_int32))))
+        return out, cnt
+
+    # ---- node types with feature slots ---------------------------------------------------------------
+    def add_nodes(self, ids, features: Sequence[Sequence] | None = None, ntype: int = 0) -> None:
+        """``features[i]`` = list of ``(slot, feasign)`` pairs of node ``ids[i]``."""
+        q = np.ascontiguousarray(ids, dtype=np.uint64)
+        if features is None:
+            N.hcheck(N.host().pbh_graph_add_nodes(self._h, ntype, _u64p(q), C.c_int64(q.size), None, None, None))
+            return
+        off = np.zeros(q.size + 1, np.int64)
+        off[1:] = np.cumsum([len(f) for f in features])
+        sl = np.ascontiguousarray([p[0] for f in features for p in f], dtype=np.int32)
+        va = np.ascontiguousarray([p[1] for f in features for p in f], dtype=np.uint64)
+        N.hcheck(N.host().pbh_graph_add_nodes(self._h, ntype, _u64p(q), C.c_int64(q.size),
+                                              off.ctypes.data_as(C.POINTER(C.c_int64)),
+                                              sl.ctypes.data_as(C.POINTER(C.c_int32)), _u64p(va)))
+
+    def load_node_file(self, path: str, ntype: int = 0, type_name: str = "", sep: str = " ") -> int:
+        """Lines ``<type name>\t<id>[\t<slot>:<v>[<sep><v>...]]...``; only lines of ``type_name`` when given."""
+        n = C.c_int64()
+        N.hcheck(N.host().pbh_graph_load_node_file(self._h, ntype, path.encode(), type_name.encode(),
+                                                   C.c_char(sep.encode()[:1]), C.byref(n)))
+        return n.value
+
+    def typed_nodes(self, ntype: int = 0) -> np.ndarray:
+        N.host().pbh_graph_num_typed_nodes.restype = C.c_int64
+        out = np.empty(N.host().pbh_graph_num_typed_nodes(self._h, ntype), np.uint64)
+        N.hcheck(N.host().pbh_graph_export_typed_nodes(self._h, ntype, _u64p(out)))
+        return out
+
+    def node_features(self, nodes, slots: Sequence[int], ntype: int = 0) -> np.ndarray:
+        """``get_feature_of_nodes``: uint64 [n, len(slots)], the first feasign of every slot (0 = none)."""
+        q = np.ascontiguousarray(nodes, dtype=np.uint64)
+        sl = np.ascontiguousarray(slots, dtype=np.int32)
+        out = np.empty((q.size, sl.size), np.uint64)
+        N.hcheck(N.host().pbh_graph_node_features(self._h, ntype, _u64p(q), C.c_int64(q.size),
+                                                  sl.ctypes.data_as(C.POINTER(C.c_int32)), int(sl.size), _u64p(out)))
+        return out
+
+    def all_feature_ids(self, ntype: int = 0) -> np.ndarray:
+        n = C.c_int64()
+        N.hcheck(N.host().pbh_graph_all_feature_ids(self._h, ntype, None, C.byref(n)))
+        out = np.empty(n.value, np.uint64)
+        N.hcheck(N.host().pbh_graph_all_feature_ids(self._h, ntype, _u64p(out), C.byref(n)))
+        return out
+
+    def load_node_weight(self, path: str, ntype: int = 0) -> int:
+        n = C.c_int64()
+        N.hcheck(N.host().pbh_graph_load_node_weight(self._h, ntype, path.encode(), C.byref(n)))
+        return n.value
+
+    def node_weights(self, nodes, ntype: int = 0) -> np.ndarray:
+        q = np.ascontiguousarray(nodes, dtype=np.uint64)
+        out = np.empty(q.size, np.float32)
+        N.hcheck(N.host().pbh_graph_node_weights(self._h, ntype, _u64p(q), C.c_int64(q.size),
+                                                 out.ctypes.data_as(C.POINTER(C.c_float))))
+        return out
+
+    # ---- partitions (paging a graph that does not fit in HBM) ---------------------------------------
+    def make_partitions(self, etype: int, byte_size: int, device_len: int = 1) -> int:
+        n = C.c_int()
+        N.hcheck(N.host().pbh_graph_make_partitions(self._h, etype, C.c_int64(byte_size), device_len, C.byref(n)))
+        return n.value
+
+    def partition_num(self, etype: int = 0) -> int:
+        return N.host().pbh_graph_partition_num(self._h, etype)
+
+    def next_partition(self, etype: int = 0) -> int:
+        """Index of the partition to page in next; -1 once after the last (then the cycle restarts)."""
+        return N.host().pbh_graph_next_partition(self._h, etype)
+
+    def partition(self, etype: int, part: int):
+        """(node_ids uint64 [n], row_ptr int64 [n+1], neighbour ids uint64 [m], weights fp32 [m] | None)."""
+        nn, ne = C.c_int64(), C.c_int64()
+        N.hcheck(N.host().pbh_graph_partition_shape(self._h, etype, part, C.byref(nn), C.byref(ne)))
+        ids = np.empty(nn.value, np.uint64)
+        rp = np.empty(nn.value + 1, np.int64)
+        col = np.empty(ne.value, np.uint64)
+        w = np.empty(ne.value, np.float32) if self.is_weighted(etype) else None
+        N.hcheck(N.host().pbh_graph_export_partition(self._h, etype, part, _u64p(ids),
+                                                     rp.ctypes.data_as(C.POINTER(C.c_int64)), _u64p(col),
+                                                     w.ctypes.data_as(C.POINTER(C.c_float)) if w is not None else None))
+        return ids, rp, col, w
+
+    def export_partition_files(self, etype: int, directory: str) -> None:
+        import os
+        os.makedirs(directory, exist_ok=True)
+        N.hcheck(N.host().pbh_graph_export_partition_files(self._h, etype, directory.encode()))
+
 
 class DeviceGraph:
     """CSR of every edge type as tensors on one device; sampling and walking are gathers there.
@@ -251,10 +373,14 @@ class GraphGpuWrapper:
     def __init__(self):
         self.table = GraphTable()
         self.edge_types: dict = {}
+        self.node_types: dict = {}
+        self.feature_separator = " "
+        self.resident_partition = -1
         self.device_graph: DeviceGraph | None = None
 
     def set_up_types(self, edge_types: Sequence[str], node_types: Sequence[str] = ()) -> None:
         self.edge_types = {name: i for i, name in enumerate(edge_types)}
+        self.node_types = {name: i for i, name in enumerate(node_types)}
 
     def load_edge_file(self, name: str, filepath: str, reverse: bool = False) -> int:
         t = self.edge_types.setdefault(name, len(self.edge_types))
@@ -269,6 +395,62 @@ class GraphGpuWrapper:
 
     def get_all_id(self, name: str) -> np.ndarray:
         return self.table.all_ids(self.edge_types[name])
+
+    # ---- node files / features / partitions: the rest of graph_gpu_wrapper.h:50-99 ------------------------
+    def load_node_file(self, name: str, filepath: str) -> int:
+        t = self.node_types.setdefault(name, len(self.node_types))
+        return self.table.load_node_file(filepath, t, name, self.feature_separator)
+
+    def set_feature_separator(self, ch: str) -> None:
+        self.feature_separator = ch
+
+    def get_feature_of_nodes(self, name: str, nodes, slots: Sequence[int]) -> np.ndarray:
+        return self.table.node_features(nodes, slots, self.node_types[name])
+
+    def get_all_feature_ids(self, name: str) -> np.ndarray:
+        return self.table.all_feature_ids(self.node_types[name])
+
+    def load_node_weight(self, name: str, path: str) -> int:
+        return self.table.load_node_weight(path, self.node_types[name])
+
+    def make_partitions(self, name: str, byte_size: int, device_len: int = 1) -> int:
+        t = self.edge_types[name]
+        self.table.build(t) if self.table.num_nodes(t) == 0 else None
+        return self.table.make_partitions(t, byte_size, device_len)
+
+    def get_partition_num(self, name: str) -> int:
+        return self.table.partition_num(self.edge_types[name])
+
+    def get_partition(self, name: str, num: int) -> np.ndarray:
+        return self.table.partition(self.edge_types[name], num)[0]
+
+    def load_next_partition(self, name: str, device=None) -> int:
+        """Pages the next partition of the edge type into HBM (it replaces the resident one); returns its index,
+        -1 when the cycle is complete.  Neighbour ids that live in another partition stay valid ids: a walk that
+        leaves the resident partition ends there, as with the reference's paged graph."""
+        t = self.edge_types[name]
+        p = self.table.next_partition(t)
+        if p < 0:
+            return -1
+        ids, rp, col_ids, _ = self.table.partition(t, p)
+        # resident CSR in the partition's own index space; edges to neighbours outside the partition are dropped
+        if ids.size and col_ids.size:
+            pos = np.minimum(np.searchsorted(ids, col_ids), ids.size - 1)
+            keep = ids[pos] == col_ids
+            row_of_edge = np.repeat(np.arange(ids.size), np.diff(rp))
+            new_rp = np.zeros(ids.size + 1, np.int64)
+            new_rp[1:] = np.cumsum(np.bincount(row_of_edge[keep], minlength=ids.size))
+            col = pos.astype(np.int64)
+        else:
+            keep = np.zeros(col_ids.size, bool)
+            new_rp = np.zeros(ids.size + 1, np.int64)
+            col = np.zeros(col_ids.size, np.int64)
+        self.device_graph = DeviceGraph({t: (ids, new_rp, col[keep])}, device)
+        self.resident_partition = p
+        return p
+
+    def export_partition_files(self, name: str, file_path: str) -> None:
+        self.table.export_partition_files(self.edge_types[name], file_path)
 
     def graph_neighbor_sample(self, name: str, nodes, sample_size: int):
         t = self.edge_types[name]

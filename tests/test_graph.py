@@ -113,3 +113,76 @@ def test_skipgram_trains_on_walk_pairs():
         box.end_pass()
     finally:
         BoxWrapper.reset_instance()
+
+
+def test_weighted_edges_node_features_and_partitions(tmp_path):
+    """The rest of the graph engine's surface (graph_gpu_wrapper.h:50-99): weighted sampling, node files with
+    feature slots, node weights, partitions for paging."""
+    from paddlebox_b200.graph import GraphGpuWrapper, GraphTable
+    g = GraphTable()
+    # node 1 has 6 neighbours; neighbour 16 carries almost all the weight
+    dst = np.array([11, 12, 13, 14, 15, 16], np.uint64)
+    w = np.array([1, 1, 1, 1, 1, 500], np.float32)
+    g.add_weighted_edges(np.full(6, 1, np.uint64), dst, w)
+    g.add_weighted_edges(np.array([2, 2], np.uint64), np.array([11, 12], np.uint64), np.array([1.0, 3.0], np.float32))
+    g.build(0)
+    assert g.is_weighted(0)
+    ids, rp, col = g.csr(0)
+    ew = g.edge_weights(0)
+    i1 = int(np.searchsorted(ids, 1))
+    assert sorted(ew[rp[i1]:rp[i1 + 1]].tolist()) == [1, 1, 1, 1, 1, 500]
+    hits = 0
+    for seed in range(200):
+        out, cnt = g.sample_neighbors_weighted(np.array([1], np.uint64), 2, 0, seed)
+        assert cnt[0] == 2 and len(set(out[0].tolist())) == 2 and set(out[0].tolist()) <= set(dst.tolist())
+        hits += 16 in out[0].tolist()
+    assert hits > 190                                   # the heavy neighbour is (nearly) always drawn
+    out, cnt = g.sample_neighbors_weighted(np.array([2, 99], np.uint64), 4, 0, 1)
+    assert cnt.tolist() == [2, 0] and sorted(out[0][:2].tolist()) == [11, 12]
+    # node file with feature slots
+    nf = tmp_path / "nodes.txt"
+    nf.write_text("user\t1\t101:7001\t102:8001 8002\nuser\t2\t101:7002\nitem\t11\t201:9001\nuser\t3\n")
+    assert g.load_node_file(str(nf), 0, "user", " ") == 3
+    assert g.load_node_file(str(nf), 1, "item", " ") == 1
+    assert g.typed_nodes(0).tolist() == [1, 2, 3] and g.typed_nodes(1).tolist() == [11]
+    f = g.node_features(np.array([2, 1, 3, 77], np.uint64), [101, 102], 0)
+    assert f.tolist() == [[7002, 0], [7001, 8001], [0, 0], [0, 0]]
+    assert g.all_feature_ids(0).tolist() == [7001, 7002, 8001, 8002]
+    wf = tmp_path / "w.txt"
+    wf.write_text("1\t2.5\n3\t0.5\n42\t9\n")
+    assert g.load_node_weight(str(wf), 0) == 2
+    assert g.node_weights(np.array([1, 2, 3, 42], np.uint64), 0).tolist() == [2.5, 1.0, 0.5, 0.0]
+    # partitions: a chain graph cut into pieces by a byte budget
+    h = GraphTable()
+    n = 1000
+    h.add_edges(np.arange(n, dtype=np.uint64), (np.arange(n, dtype=np.uint64) + 1) % n)
+    h.build(0)
+    parts = h.make_partitions(0, 32 * 100, 1)           # 32 bytes per node with one edge -> 100 nodes per partition
+    assert parts == 10 and h.partition_num(0) == 10
+    seen = []
+    while True:
+        p = h.next_partition(0)
+        if p < 0:
+            break
+        ids, rp, col_ids, wts = h.partition(0, p)
+        assert wts is None and ids.size == 100 and rp[-1] == 100 and np.array_equal(col_ids, (ids + 1) % n)
+        seen.extend(ids.tolist())
+    assert seen == list(range(n)) and h.next_partition(0) == 0      # the cycle restarts
+    h.export_partition_files(0, str(tmp_path / "parts"))
+    assert (tmp_path / "parts" / "partition_9").read_text().split()[:2] == ["900", "901"]
+    # the reference's wrapper names
+    wpr = GraphGpuWrapper()
+    wpr.set_up_types(["u2i"], ["user", "item"])
+    ef = tmp_path / "e.txt"
+    ef.write_text("".join(f"{i}\t{(i + 1) % 50}\n" for i in range(50)))
+    wpr.load_edge_file("u2i", str(ef))
+    wpr.table.build(0)
+    assert wpr.load_node_file("user", str(nf)) == 3 and wpr.get_all_feature_ids("user").tolist() == [7001, 7002, 8001, 8002]
+    assert wpr.get_feature_of_nodes("user", np.array([1], np.uint64), [102]).tolist() == [[8001]]
+    assert wpr.make_partitions("u2i", 32 * 10, 1) == 5 and wpr.get_partition_num("u2i") == 5
+    assert wpr.get_partition("u2i", 1).tolist() == list(range(10, 20))
+    p0 = wpr.load_next_partition("u2i", device="cpu")
+    assert p0 == 0 and wpr.resident_partition == 0
+    dg = wpr.device_graph
+    nb, cnt = dg.sample_neighbors(torch.tensor([3, 9], dtype=torch.int64), 2, 0)
+    assert cnt.tolist() == [1, 0] and int(nb[0, 0]) == 4       # 9 -> 10 leaves the resident partition: dropped
