@@ -511,3 +511,21 @@ def cpu_train_from_dataset_sharded(rank, world, data_dir):
     stats = trainer.train_from_dataset(ds)
     ds.end_pass(False)
     return {"loaded": int(loaded), "instances": int(stats["instances"]), "steps": int(stats["steps"])}
+
+
+def cpu_legacy_global_shuffle(rank, world):
+    """Record-based global shuffle: every record travels to hash(ins_id) % world in the Record wire format."""
+    from paddlebox_b200 import legacy_feed as LF
+    ds = LF.MultiSlotDataset(["uint64", "float"], batch_size=4)
+    ds.set_trainer(rank, world)
+    ds.records = [LF.Record(np.array([1000 * rank + i], np.uint64), np.zeros(1, np.uint16), np.array([0.5], np.float32),
+                            np.ones(1, np.uint16), f"ins{rank}_{i}") for i in range(50 + 10 * rank)]
+    before = len(ds.records)
+    after = ds.global_shuffle(seed=3)
+    ids = sorted(r.ins_id for r in ds.records)
+    import hashlib
+    ok_owner = all(int.from_bytes(hashlib.md5(i.encode()).digest()[:8], "little") % world == rank for i in ids)
+    tot = torch.tensor([before, after], dtype=torch.int64)
+    dist.all_reduce(tot)
+    return {"before": before, "after": after, "total_before": int(tot[0]), "total_after": int(tot[1]), "owner_ok": ok_owner,
+            "sum_signs": int(sum(int(r.u64_signs[0]) for r in ds.records))}

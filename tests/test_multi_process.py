@@ -114,6 +114,13 @@ def test_train_from_dataset_trains_every_local_record_two_ranks(tmp_path):
     assert outs[0]["steps"] == outs[1]["steps"] == 13                               # ceil(200 / 16), equalised
 
 
+def test_legacy_record_global_shuffle_two_ranks_gloo():
+    outs = _spawn(W.cpu_legacy_global_shuffle, 2, "gloo")
+    assert outs[0]["total_before"] == outs[0]["total_after"] == 110 and all(o["owner_ok"] for o in outs)
+    assert outs[0]["after"] + outs[1]["after"] == 110 and outs[0]["after"] not in (0, 110)
+    assert outs[0]["sum_signs"] + outs[1]["sum_signs"] == sum(range(50)) + sum(1000 + i for i in range(60))
+
+
 def _ngpu():
     return torch.cuda.device_count() if torch.cuda.is_available() else 0
 
