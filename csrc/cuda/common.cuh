@@ -37,10 +37,10 @@ void pbx_note_launch(int n);
   } while (0)
 
 static inline int pbx_num_sms() {
-  static int sms[16] = {0};
+  static int sms[64] = {0};     // same bound as kMaxDevices of the allocation-free entry point
   int dev = 0;
   cudaGetDevice(&dev);
-  if (dev < 0 || dev >= 16) dev = 0;
+  if (dev < 0 || dev >= 64) dev = 0;
   if (sms[dev] == 0) {
     cudaDeviceGetAttribute(&sms[dev], cudaDevAttrMultiProcessorCount, dev);
     if (sms[dev] <= 0) sms[dev] = 148;

@@ -551,11 +551,14 @@ int launch_tc(const __nv_bfloat16* A, int lda, const __nv_bfloat16* B, int ldb, 
   if (splitk > num_kb) splitk = num_kb;
   const int kb_per = (num_kb + splitk - 1) / splitk;
   splitk = (num_kb + kb_per - 1) / kb_per;
-  static bool attr_set = false;
-  if (!attr_set) {
+  // (the attribute is per DEVICE: one flag per device ordinal, for processes that drive several GPUs)
+  static bool attr_set[64] = {false};
+  int dev_ord = 0;
+  cudaGetDevice(&dev_ord);
+  if (dev_ord < 0 || dev_ord >= 64 || !attr_set[dev_ord]) {
     PBX_CUDA_CHECK(cudaFuncSetAttribute(k_gemm_tcgen05<BN, STG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         SmemLayout<BN, STG>::TOTAL));
-    attr_set = true;
+    if (dev_ord >= 0 && dev_ord < 64) attr_set[dev_ord] = true;
   }
   dim3 grid((M + BM - 1) / BM, (N + BN - 1) / BN, splitk);
   k_gemm_tcgen05<BN, STG><<<grid, GEMM_THREADS, SmemLayout<BN, STG>::TOTAL, st>>>(ma, mb, M, N, K, kb_per, ep);
@@ -565,7 +568,7 @@ int launch_tc(const __nv_bfloat16* A, int lda, const __nv_bfloat16* B, int ldb, 
 
 template <int BN>
 int launch_grouped(const PbxGemmProblem* pr, int n, cudaStream_t st) {
-  static GroupedGemm g;     // ~3 KB: filled on the host, passed by value
+  static thread_local GroupedGemm g;     // ~3 KB per calling thread: filled on the host, passed by value
   memset(&g, 0, sizeof(g));
   g.n = n;
   int ctas = 0;
@@ -598,11 +601,13 @@ int launch_grouped(const PbxGemmProblem* pr, int n, cudaStream_t st) {
     ctas += g.gx[i] * g.gy[i] * splitk;
     g.cta_end[i] = ctas;
   }
-  static bool attr_set = false;
-  if (!attr_set) {
+  static bool attr_set[64] = {false};
+  int dev_ord = 0;
+  cudaGetDevice(&dev_ord);
+  if (dev_ord < 0 || dev_ord >= 64 || !attr_set[dev_ord]) {
     PBX_CUDA_CHECK(cudaFuncSetAttribute(k_gemm_tcgen05_grouped<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                         SmemLayout<BN, GroupedStages<BN>::value>::TOTAL));
-    attr_set = true;
+    if (dev_ord >= 0 && dev_ord < 64) attr_set[dev_ord] = true;
   }
   k_gemm_tcgen05_grouped<BN><<<ctas, GEMM_THREADS, SmemLayout<BN, GroupedStages<BN>::value>::TOTAL, st>>>(g);
   PBX_CUDA_CHECK(cudaGetLastError()); pbx_note_launch(1);

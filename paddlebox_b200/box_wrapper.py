@@ -237,21 +237,29 @@ class BoxWrapper:
             # streamed build (pass_build.py): host fetch of chunk k+1 into a pinned slot overlaps the H2D copy
             # and the insert kernel of chunk k; staging memory is a fixed pool reused by every pass
             # (ps_gpu_wrapper.cc:684-955, heter_comm_inl.h:671-731, mem_pool.h:28-102)
-            self.last_pass_build = self.pass_builder().build(keys) if keys.size else {}
+            self.last_pass_build = self.pass_builder(int(keys.size)).build(keys) if keys.size else {}
         else:
             if keys.size:
                 self.host_table.fetch_rows(keys, create=True)  # create missing rows
         self._in_pass = True
         self.timers.add("begin_pass", time.time() - t0)
 
-    def pass_builder(self):
-        """The pass build / write-back pipeline of this shard (created on first use, staging pool reused)."""
+    def pass_builder(self, n_rows: int = 0):
+        """The pass build / write-back pipeline of this shard.  Its pinned staging pool is kept across passes and
+        only re-made when a pass needs larger slots than any before (up to ``FLAGS.pbx_pass_chunk_rows`` rows per
+        slot), so small jobs do not pin hundreds of megabytes."""
+        want = int(FLAGS.pbx_pass_chunk_rows)
+        if n_rows > 0:
+            c = 1024
+            while c < n_rows and c < want:
+                c <<= 1
+            want = min(want, c)
         pb = getattr(self, "_pass_builder", None)
-        if pb is None:
+        if pb is None or (n_rows > 0 and pb.pool.chunk < want):
             from .pass_build import PassBuilder
             pb = self._pass_builder = PassBuilder(self.host_table, self.table.insert, self.host_table.layout.stride,
-                                                  self.device, chunk=int(FLAGS.pbx_pass_chunk_rows),
-                                                  depth=3, fetch_threads=int(FLAGS.pbx_pass_fetch_threads))
+                                                  self.device, chunk=want, depth=3,
+                                                  fetch_threads=int(FLAGS.pbx_pass_fetch_threads))
         return pb
 
     def end_pass(self, need_save_delta: bool = False, delta_path: str = "") -> None:
@@ -263,7 +271,7 @@ class BoxWrapper:
             dk, dr = self.table.dump(only_dirty=True, clear_dirty=True)
             if dk.numel():
                 # bounded pinned chunks: D2H of chunk k+1 overlaps the host-table store of chunk k
-                self.last_pass_write_back = self.pass_builder().write_back(dk, dr, mark_dirty=True)
+                self.last_pass_write_back = self.pass_builder(int(dk.numel())).write_back(dk, dr, mark_dirty=True)
         self._in_pass = False
         if need_save_delta and delta_path:
             self.save_delta(delta_path)
@@ -311,7 +319,7 @@ class BoxWrapper:
             dk, dr = self.table.dump(only_dirty=True, clear_dirty=True)
             if dk.numel():
                 # bounded pinned chunks: D2H of chunk k+1 overlaps the host-table store of chunk k
-                self.last_pass_write_back = self.pass_builder().write_back(dk, dr, mark_dirty=True)
+                self.last_pass_write_back = self.pass_builder(int(dk.numel())).write_back(dk, dr, mark_dirty=True)
 
     def save_base(self, batch_model_path: str, xbox_model_path: str = "", date: str = "") -> str:
         """Full training checkpoint ("batch model", every optimizer state) + serving base
