@@ -10,7 +10,7 @@ Per (keys, dim) the script reports, for pull and push:
   us            kernel time (max over ranks, median of iterations)
   nvlink_MB     bytes this rank must move over NVLink (keys out + values in for pull, merged
                 records out for push), counted from the routed unique keys
-  roofline_us   max(nvlink bytes / 770 GB/s measured peer-copy bandwidth, local HBM bytes / hbm_gbs)
+  roofline_us   max(nvlink bytes / 900 GB/s (NVLink 5 per direction), local HBM bytes / hbm_gbs)
   frac          roofline_us / us
   nccl_us       the same pull done as torch.unique + all_to_all_single(keys) + table lookup +
                 all_to_all_single(values) + index_select  (NCCL baseline)
@@ -28,7 +28,7 @@ import torch.distributed as dist
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
-NVLINK_GBS = 770.0   # measured peer copy, per direction (B200_PROFILING.md)
+NVLINK_GBS = 900.0   # NVLink 5 per direction per GPU: the denominator BASELINE.md / SURVEY.md §6 name
 
 
 def hbm_gbs():
@@ -58,7 +58,7 @@ def timed(fn, iters, warmup, dev):
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--keys", default="65536,1048576,4194304")
+    ap.add_argument("--keys", default="65536,1048576,4194304,16777216")   # config 5: 64 K - 16 M keys per batch
     ap.add_argument("--dims", default="8,16,64,128")
     ap.add_argument("--table-keys-per-gpu", type=int, default=20_000_000)
     ap.add_argument("--iters", type=int, default=10)
@@ -76,7 +76,7 @@ def main():
     out = []
     for dim in [int(x) for x in a.dims.split(",")]:
         for nk in [int(x) for x in a.keys.split(",")]:
-            table = SparseTable(int(a.table_keys_per_gpu / 0.6), dim, "adagrad")
+            table = SparseTable(int(a.table_keys_per_gpu / 0.75), dim, "adagrad")   # reference load factor
             table.fill_synthetic(a.table_keys_per_gpu * world, 1, rank, world)
             eng = SparseEngine(table, nk, rank, world, cap=int(2.0 * nk / world) + 4096)
             g = torch.Generator().manual_seed(rank)
