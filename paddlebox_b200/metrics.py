@@ -27,6 +27,25 @@ def parse_cmatch_rank(x: torch.Tensor):
     return (x >> 32) & 0xFFFFFFFF, x & 0xFF
 
 
+def accumulate_float_labels(table: torch.Tensor, sums: torch.Tensor, pred: torch.Tensor, label: torch.Tensor,
+                            mask: torch.Tensor | None, mode: int) -> None:
+    """Device-side twin of ``AucCalculator::add_data`` for float labels (csrc/host/metrics.cc; reference
+    fleet/metrics.cc:75-136): ``mode`` 1 = a label in [0, 1] is split fractionally between the negative and the
+    positive table; ``mode`` 2 = continuous values, only the five sums.  ``table`` fp64 [2, n], ``sums`` fp64 [5] =
+    (abs err, sq err, pred sum, label sum, count).  Runs on whatever device the tensors live on."""
+    p = pred.reshape(-1).double()
+    y = label.reshape(-1).double()
+    w = torch.ones_like(p) if mask is None else (mask.reshape(-1) != 0).double()
+    if mode != 2:
+        p = torch.nan_to_num(p, nan=0.0, posinf=1.0, neginf=0.0).clamp_(0.0, 1.0)
+        n = table.shape[1]
+        pos = (p * n).long().clamp_(max=n - 1)
+        table[0].index_add_(0, pos, (1.0 - y) * w)
+        table[1].index_add_(0, pos, y * w)
+    d = p - y
+    sums += torch.stack([(d.abs() * w).sum(), (d * d * w).sum(), (p * w).sum(), (y * w).sum(), w.sum()])
+
+
 class MetricMsg:
     def __init__(self, name="", label_varname="label", pred_varname="pred", metric_phase=1, bucket_size=1000000,
                  device=None, float_label=False, **_):
@@ -54,6 +73,13 @@ class MetricMsg:
                                             N.ptr(mask.contiguous()) if mask is not None else None,
                                             C.c_int64(pred.numel()), self.bucket_size, N.ptr(self._dev_table),
                                             N.ptr(self._dev_sums), N.stream_ptr()), "pbx_auc_bucket")
+        elif pred.is_cuda:
+            # float-label modes: accumulated on the device with a few PyTorch ops (no host sync per batch, so
+            # a captured training step keeps replaying); merged into the host calculator at read-out
+            if self._dev_table is None:
+                self._dev_table = torch.zeros(2, self.bucket_size, dtype=torch.float64, device=pred.device)
+                self._dev_sums = torch.zeros(5, dtype=torch.float64, device=pred.device)
+            accumulate_float_labels(self._dev_table, self._dev_sums, pred, label, mask, int(self.float_label))
         else:
             self.calc.add(pred.cpu().numpy(), label.cpu().numpy(), None if mask is None else mask.cpu().numpy(),
                           self.float_label)
@@ -212,12 +238,30 @@ class WuAucMetricMsg(MetricMsg):
         super().__init__(**kw)
         self.uid_varname = uid_varname
 
+    FLUSH_EVERY = 256      # batches kept on the device before one copy to the host
+
     def add_data(self, tensors):
-        self.calc.add_uid(tensors[self.pred_varname].detach().float().cpu().numpy(),
-                          tensors[self.label_varname].detach().float().cpu().numpy(),
-                          tensors[self.uid_varname].detach().cpu().numpy())
+        p, y, u = tensors[self.pred_varname].detach(), tensors[self.label_varname].detach(), tensors[self.uid_varname].detach()
+        if p.is_cuda:
+            # per-user records stay on the device; one host copy per FLUSH_EVERY batches instead of one per batch
+            buf = self.__dict__.setdefault("_pending", [])
+            buf.append((p.reshape(-1).float().clone(), y.reshape(-1).float().clone(), u.reshape(-1).clone()))
+            if len(buf) >= self.FLUSH_EVERY:
+                self._flush_uid()
+            return
+        self.calc.add_uid(p.float().cpu().numpy(), y.float().cpu().numpy(), u.cpu().numpy())
+
+    def _flush_uid(self):
+        buf = self.__dict__.get("_pending") or []
+        if buf:
+            p = torch.cat([b[0] for b in buf]).cpu().numpy()
+            y = torch.cat([b[1] for b in buf]).cpu().numpy()
+            u = torch.cat([b[2] for b in buf]).cpu().numpy()
+            buf.clear()
+            self.calc.add_uid(p, y, u)
 
     def get_metric_msg(self, group=None):
+        self._flush_uid()
         out = self.calc.compute_wuauc()   # [uauc, wuauc, user_cnt, size]
         self.calc.reset()
         return out
@@ -234,11 +278,21 @@ class NanInfMetricMsg(MetricMsg):
 
     def add_data(self, tensors):
         p = tensors[self.pred_varname].detach().reshape(-1)
+        self.total += p.numel()
+        if p.is_cuda:                       # counted on the device, read at get_nan_inf_msg: no sync per batch
+            if self.__dict__.get("_dev_cnt") is None:
+                self._dev_cnt = torch.zeros(2, dtype=torch.int64, device=p.device)
+            self._dev_cnt += torch.stack([torch.isnan(p).sum(), torch.isinf(p).sum()])
+            return
         self.nan += int(torch.isnan(p).sum())
         self.inf += int(torch.isinf(p).sum())
-        self.total += p.numel()
 
     def get_nan_inf_msg(self):
+        if self.__dict__.get("_dev_cnt") is not None:
+            c = self._dev_cnt.cpu().tolist()
+            self.nan += int(c[0])
+            self.inf += int(c[1])
+            self._dev_cnt.zero_()
         out = [self.nan, self.inf, self.total]
         self.nan = self.inf = self.total = 0
         return out

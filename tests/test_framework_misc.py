@@ -452,3 +452,34 @@ def test_vectorised_cpu_seqpool_matches_the_loop_oracle():
         db = R.seqpool_cvm_bwd_vec(dout, cvm, lod, B, S, H, **bkw)
         assert torch.equal(da, db), kw
     assert not R.seqpool_plain(dict(need_filter=True)) and not R.seqpool_plain(dict(embedx_concate_size=2))
+
+
+def test_float_label_metrics_accumulate_without_host_sync():
+    """The device-side accumulation used for float-label / continuous metrics (pure PyTorch ops, so it is checked
+    here on CPU tensors) gives the numbers of the host calculator (csrc/host/metrics.cc add_data)."""
+    from paddlebox_b200.host import HostAuc
+    from paddlebox_b200.metrics import accumulate_float_labels
+    rs = np.random.RandomState(3)
+    n, buckets = 5000, 1000
+    pred = torch.from_numpy(rs.rand(n).astype(np.float32))
+    pred[:3] = torch.tensor([float("nan"), 1.7, -0.2])
+    label = torch.from_numpy(rs.rand(n).astype(np.float32))
+    mask = torch.from_numpy((rs.rand(n) < 0.7).astype(np.float32))
+    for mode in (1, 2):
+        ref = HostAuc(buckets)
+        ref.add(pred.numpy(), label.numpy(), mask.numpy(), mode)
+        rt, rsum = ref.export_state()
+        table = torch.zeros(2, buckets, dtype=torch.float64)
+        sums = torch.zeros(5, dtype=torch.float64)
+        accumulate_float_labels(table, sums, pred[:2000], label[:2000], mask[:2000], mode)       # two batches
+        accumulate_float_labels(table, sums, pred[2000:], label[2000:], mask[2000:], mode)
+        if mode == 1:
+            assert np.allclose(table.numpy(), rt, atol=1e-9)
+            assert np.allclose(sums.numpy(), rsum, rtol=1e-9)
+        else:                                   # continuous: NaN is not clamped by either side
+            ok = ~torch.isnan(pred)
+            ref2 = HostAuc(buckets)
+            ref2.add(pred[ok].numpy(), label[ok].numpy(), mask[ok].numpy(), 2)
+            t2 = torch.zeros(2, buckets, dtype=torch.float64); s2 = torch.zeros(5, dtype=torch.float64)
+            accumulate_float_labels(t2, s2, pred[ok], label[ok], mask[ok], 2)
+            assert np.allclose(s2.numpy(), ref2.export_state()[1], rtol=1e-9) and float(t2.sum()) == 0.0
