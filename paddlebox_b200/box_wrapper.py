@@ -306,10 +306,21 @@ class BoxWrapper:
             self.router.push(R.merge_push(restore, n_unique, grads, key2slot, 2, -float(batch_size)))
             return
         if self.use_cuda:
+            if FLAGS.pbx_deterministic_merge and self.world_size == 1:
+                # sorted, fp64 segmented merge (reference PushMergeCopy, box_wrapper.cu:417-475), then the plain
+                # by-key table update: bit-reproducible whatever the key skew
+                n_rows = self.engine.n_unique_rows
+                merged = R.merge_push_sorted(restore, n_rows, grads, key2slot, 2, -float(batch_size))
+                uk = torch.zeros(n_rows, dtype=torch.int64, device=keys.device)
+                uk[restore.long()] = keys[:restore.numel()]
+                used = merged[:, 1] > 0                       # rows that received a show count
+                self.table.update(uk[used], merged[used].contiguous())
+                return
             self.engine.push_keys(restore, grads.contiguous(), key2slot, 2, -float(batch_size))
             return
         uk = self._cpu_unique
-        merged = R.merge_push(restore, uk.numel(), grads, key2slot, 2, -float(batch_size))
+        merge = R.merge_push_sorted if FLAGS.pbx_deterministic_merge else R.merge_push
+        merged = merge(restore, uk.numel(), grads, key2slot, 2, -float(batch_size))
         self.host_table.push(uk.numpy(), merged)
 
     # ---- model save / load -------------------------------------------------------------------

@@ -91,6 +91,8 @@ _d("enable_debug_print_metrics_info", False, "verbose AUC computation (metrics.c
 _d("pbx_use_cuda_graph", True, "capture the training step in a CUDA graph when shapes allow")
 _d("pbx_pack_threads", 4, "background threads packing mini-batches into staging buffers (per loader)")
 _d("pbx_overlap_wgrad", False, "weight-gradient GEMMs on a side stream, concurrently with the dgrad chain (measured: no gain over the grouped launch)")
+_d("pbx_deterministic_merge", False, "push gradients merged by a stable sort + fp64 segmented sum (bit-reproducible, "
+   "robust to hot keys) instead of the in-kernel merge; single-rank GPU jobs and the CPU path")
 _d("pbx_pass_chunk_rows", 1 << 19, "rows per staging slot of the pass build / write-back pipeline (3 pinned slots)")
 _d("pbx_pass_fetch_threads", 4, "CPU threads fetching host-table rows into pinned staging slots during begin_pass")
 _d("pbx_fold_dense_allreduce", True, "data-parallel dense-gradient allreduce rides on the sparse push kernel's barriers")

@@ -207,8 +207,9 @@ class _SparseEmbeddingPool(torch.autograd.Function):
         nothing = (None, None, None, None, None, None)    # the anchor only keeps the node alive
         if box._test_mode:
             return nothing
+        from ..flags import FLAGS
         fused_ok = (dout.is_cuda and box.router is None and attrs.cvm_offset == 2 and attrs.embedx_concate_size == 1
-                    and attrs.variant == 0)
+                    and attrs.variant == 0 and not FLAGS.pbx_deterministic_merge)
         if fused_ok:
             Eo = attrs.out_width(box.hidden)
             if dout.stride(1) != 1:

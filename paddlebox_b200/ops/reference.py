@@ -313,6 +313,29 @@ def dedup_keys_and_fillidx(keys: torch.Tensor):
     return merged, restore, sorted_idx, offset, cnts
 
 
+def merge_push_sorted(restore: torch.Tensor, n_unique: int, grads: torch.Tensor, key2slot: torch.Tensor,
+                      cvm_offset: int, grad_scale: float) -> torch.Tensor:
+    """Deterministic twin of ``merge_push``: the occurrences are sorted by unique row (stable) and every row's
+    gradients are summed in fp64 in that fixed order — the reference's segmented merge (PushMergeCopy,
+    box_wrapper.cu:417-475: sorted index, fp64 accumulation), chosen there for batches with hot keys.  The slot id
+    of a row is that of its first occurrence.  Works on any device; no atomics."""
+    H = grads.shape[1]
+    r = restore.long().reshape(-1)
+    out = torch.zeros(n_unique, H + 1, dtype=torch.float64, device=grads.device)
+    if r.numel() == 0:
+        return out.float()
+    order = torch.argsort(r, stable=True)
+    rs = r[order]
+    g = grads.double()[order]
+    g[:, cvm_offset:] *= grad_scale
+    uniq, counts = torch.unique_consecutive(rs, return_counts=True)
+    sums = torch.segment_reduce(g, "sum", lengths=counts, axis=0)
+    starts = torch.cumsum(counts, 0) - counts
+    out[uniq, 1:] = sums
+    out[uniq, 0] = key2slot.reshape(-1)[order][starts].double()
+    return out.float()
+
+
 def merge_push(restore: torch.Tensor, n_unique: int, grads: torch.Tensor, key2slot: torch.Tensor, cvm_offset: int,
                grad_scale: float) -> torch.Tensor:
     """Push records [U, 4 + D] = [slot, show, clk, embed_g, embedx_g] merged by key

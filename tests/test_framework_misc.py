@@ -483,3 +483,63 @@ def test_float_label_metrics_accumulate_without_host_sync():
             t2 = torch.zeros(2, buckets, dtype=torch.float64); s2 = torch.zeros(5, dtype=torch.float64)
             accumulate_float_labels(t2, s2, pred[ok], label[ok], mask[ok], 2)
             assert np.allclose(s2.numpy(), ref2.export_state()[1], rtol=1e-9) and float(t2.sum()) == 0.0
+
+
+def test_sorted_merge_matches_atomic_merge_under_key_skew():
+    """Hot-key batch: 30 % of the occurrences are one key, plus the padding key 0 — the sorted fp64 merge
+    (reference PushMergeCopy) and the index_add merge agree, and the sorted one is bit-reproducible."""
+    from paddlebox_b200.ops import reference as R
+    g = torch.Generator().manual_seed(9)
+    n, H, S = 6000, 11, 5
+    keys = torch.randint(1, 400, (n,), generator=g)
+    keys[torch.rand(n, generator=g) < 0.30] = 77          # the hot key
+    keys[:50] = 0                                         # padding key
+    uk, restore = torch.unique(keys, return_inverse=True)
+    grads = torch.randn(n, H, generator=g)
+    grads[:, 0] = 1.0
+    grads[:, 1] = (torch.rand(n, generator=g) < 0.2).float()
+    k2s = torch.randint(0, S, (n,), generator=g)
+    a = R.merge_push(restore, uk.numel(), grads, k2s, 2, -64.0)
+    b = R.merge_push_sorted(restore, uk.numel(), grads, k2s, 2, -64.0)
+    assert torch.allclose(a[:, 1:], b[:, 1:], rtol=1e-5, atol=1e-4)
+    hot = int((uk == 77).nonzero())
+    assert abs(float(b[hot, 1]) - float((keys == 77).sum())) < 1e-3          # show count of the hot key
+    perm = torch.randperm(n, generator=g)                                     # another occurrence order
+    c = R.merge_push_sorted(restore[perm], uk.numel(), grads[perm], k2s[perm], 2, -64.0)
+    assert torch.allclose(b[:, 1:], c[:, 1:], rtol=1e-6, atol=1e-5)
+    again = R.merge_push_sorted(restore, uk.numel(), grads, k2s, 2, -64.0)
+    assert torch.equal(b, again)                                               # bit-reproducible
+    first = torch.tensor([int((restore == u).nonzero()[0]) for u in range(uk.numel())])
+    assert torch.equal(b[:, 0], k2s[first].float())                            # slot of the first occurrence
+
+
+def test_cpu_training_with_deterministic_merge_flag(tmp_path):
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    from paddlebox_b200.flags import FLAGS
+    from paddlebox_b200.models.ctr import CtrDnn
+    from paddlebox_b200.ops.pull_box_sparse import SlotBatch
+    from paddlebox_b200.trainer import CTRTrainer
+
+    def run(flag):
+        BoxWrapper.reset_instance()
+        FLAGS.pbx_deterministic_merge = flag
+        try:
+            box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=0, world_size=1)
+            box.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0})
+            g = torch.Generator().manual_seed(1)
+            keys = torch.randint(1, 30, (96,), generator=g)
+            keys[::3] = 7
+            lod = torch.arange(0, 97, 2, dtype=torch.int32)          # 48 bags of 2 keys: 2 slots x 24 instances
+            dense = torch.rand(24, 2, generator=g); dense[:, 0] = (dense[:, 0] < 0.3).float()
+            b = SlotBatch(keys, lod, 24, 2, dense)
+            box.begin_feed_pass("20240101"); box.feed_pass(keys); box.end_feed_pass(); box.begin_pass()
+            torch.manual_seed(0)
+            tr = CTRTrainer(CtrDnn(num_slots=2, embedx_dim=4, dense_dim=1, hidden=(8,)), box)
+            losses = [float(tr.train_step(b).detach()) for _ in range(6)]
+            box.end_pass()
+            return losses
+        finally:
+            FLAGS.pbx_deterministic_merge = False
+            BoxWrapper.reset_instance()
+    a, b = run(False), run(True)
+    assert np.allclose(a, b, rtol=1e-4, atol=1e-5) and run(True) == b
