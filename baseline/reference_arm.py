@@ -281,6 +281,19 @@ def run(args) -> int:
     lib.ref_set_compute_stream.argtypes = [C.c_int, C.c_void_p]
     lib.ref_destroy.argtypes = [C.c_void_p]
 
+    # watchdog (armed before the table build and ncclCommInitAll, which can stall too): a run that does not finish in
+    # time reports itself unavailable instead of hanging the caller
+    deadline_s = float(os.environ.get("PBX_REF_DEADLINE_S", 180 + 20 * ndev))
+    finished = threading.Event()
+
+    def watchdog():
+        if not finished.wait(deadline_s):
+            print(json.dumps({"impl": "reference", "n_gpus": ndev,
+                              "unavailable": f"reference arm did not finish within {int(deadline_s)} s at {ndev} GPUs "
+                                             "(HeterComm worker threads stalled)"}), flush=True)
+            os._exit(0)
+    threading.Thread(target=watchdog, daemon=True).start()
+
     B, S = args.batch, args.slots
     hidden = tuple(int(x) for x in args.hidden.split(","))
     for d in range(ndev):
@@ -295,18 +308,6 @@ def run(args) -> int:
     fill_s = time.time() - t0
     if ndev > 1 and lib.ref_nccl_init(h) != 0:
         return unavailable("ncclCommInitAll failed: " + lib.ref_last_error().decode()[:200])
-
-    # watchdog: a run that does not finish in time reports itself unavailable instead of hanging the caller
-    deadline_s = float(os.environ.get("PBX_REF_DEADLINE_S", 120 + 15 * ndev))
-    finished = threading.Event()
-
-    def watchdog():
-        if not finished.wait(deadline_s):
-            print(json.dumps({"impl": "reference", "n_gpus": ndev,
-                              "unavailable": f"reference arm did not finish within {int(deadline_s)} s at {ndev} GPUs "
-                                             "(HeterComm worker threads stalled)"}), flush=True)
-            os._exit(0)
-    threading.Thread(target=watchdog, daemon=True).start()
 
     workers = [Worker(d, args, lib, h, ndev, hidden) for d in range(ndev)]
     nccl_barrier = threading.Barrier(ndev)
