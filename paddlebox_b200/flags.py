@@ -95,6 +95,8 @@ _d("pbx_deterministic_merge", False, "push gradients merged by a stable sort + f
    "robust to hot keys) instead of the in-kernel merge; single-rank GPU jobs and the CPU path")
 _d("pbx_pass_chunk_rows", 1 << 19, "rows per staging slot of the pass build / write-back pipeline (3 pinned slots)")
 _d("pbx_pass_fetch_threads", 4, "CPU threads fetching host-table rows into pinned staging slots during begin_pass")
+_d("pbx_dense_overlap_mb", 0.0, "> 0: the dense-gradient allreduce runs in buckets of this many MB, each started from an autograd hook as soon as its gradients are final, on a side stream under the rest of backward (large dense models; takes precedence over the fold)")
+_d("pbx_dense_overlap_bf16", False, "overlapped dense allreduce: gradients travel as bf16 (cast before, cast back + scale after)")
 _d("pbx_fold_dense_allreduce", True, "data-parallel dense-gradient allreduce rides on the sparse push kernel's barriers")
 _d("pbx_sparse_dist", False, "GPU worlds: route pull/push through torch.distributed all-to-all (multi-node) instead of the one-node peer-memory engine; CPU worlds with > 1 rank always route this way")
 _d("pbx_sparse_cap_factor", 2.0, "mailbox capacity = factor * max_keys / nranks")

@@ -214,6 +214,124 @@ class DenseOptimizer:
         s.mark_dirty()
 
 
+class OverlappedGradReducer:
+    """Bucketed dense-gradient allreduce that runs UNDER backward.
+
+    The reference reduces the fused dense buffer once per step after the whole backward
+    (boxps_worker.cc:1191-1258; c_mixallgather_op.cc:209-328 packs, then reduces).  For a tower with hundreds
+    of MB of parameters that leaves the whole transfer exposed.  Here the flat gradient buffer is cut into
+    buckets of consecutive parameters (taken in reverse registration order, the order backward produces
+    them); a post-accumulate hook on every parameter counts its bucket down, and a bucket whose gradients
+    are all final is reduced at once on a side stream while autograd keeps producing the earlier layers.
+    Buckets start in a fixed order on every rank (bucket i never before bucket i-1), so the ranks issue the
+    same collectives in the same order whatever the hook timing.
+
+    Transport per bucket: the scale-fused one-kernel collective over symmetric memory when the store has
+    one (``symm.allreduce(off, n, scale, stream=side)``), else ``torch.distributed.all_reduce(async_op=True)``
+    (NCCL on GPUs, gloo on CPU) — optionally on a bf16 copy of the bucket (``cast_bf16``: half the bytes;
+    cast back and scale in one pass)."""
+
+    def __init__(self, store: "DenseParamStore", bucket_bytes: int, cast_bf16: bool = False):
+        self.store, self.cast = store, bool(cast_bf16)
+        self.scale = 1.0 / store.nranks
+        self.side = torch.cuda.Stream(device=store.device) if store.cuda else None
+        # buckets over the flat buffer: [lo, hi) element ranges of consecutive parameters, last parameter first
+        self.buckets: list[dict] = []
+        cur_hi, cur_lo, cnt = None, None, 0
+        ends = [o + (p.numel() + 3) // 4 * 4 for p, o in zip(store.params, store.offsets)]
+        self.bucket_of = {}
+        for i in range(len(store.params) - 1, -1, -1):
+            if cur_hi is None:
+                cur_hi = ends[i]
+            cur_lo = store.offsets[i]
+            cnt += 1
+            self.bucket_of[id(store.params[i])] = len(self.buckets)
+            if (cur_hi - cur_lo) * 4 >= bucket_bytes or i == 0:
+                self.buckets.append({"lo": cur_lo, "hi": cur_hi, "n_params": cnt, "pending": cnt})
+                cur_hi, cnt = None, 0
+        self.next = 0
+        self.inflight: list = []
+        self.launched_in_backward = 0          # buckets started from hooks in the last step (overlap evidence)
+        self.handles = [p.register_post_accumulate_grad_hook(self._hook) for p in store.params]
+        if self.cast:
+            self.bf = torch.empty(store.numel, dtype=torch.bfloat16, device=store.device)
+
+    def remove(self) -> None:
+        for h in self.handles:
+            h.remove()
+        self.handles = []
+
+    def begin_step(self) -> None:
+        for b in self.buckets:
+            b["pending"] = b["n_params"]
+        self.next = 0
+        self.inflight.clear()
+        self.launched_in_backward = 0
+
+    def _hook(self, p) -> None:
+        b = self.buckets[self.bucket_of[id(p)]]
+        b["pending"] -= 1
+        started = self._start_ready()
+        self.launched_in_backward += started
+
+    def _start_ready(self, force: bool = False) -> int:
+        n = 0
+        while self.next < len(self.buckets) and (force or self.buckets[self.next]["pending"] <= 0):
+            self._launch(self.buckets[self.next])
+            self.next += 1
+            n += 1
+        return n
+
+    def _launch(self, b: dict) -> None:
+        s = self.store
+        lo, n = b["lo"], b["hi"] - b["lo"]
+        view = s.gflat[lo:lo + n]
+        if s.cuda:
+            self.side.wait_stream(torch.cuda.current_stream(s.device))      # the bucket's gradients are final
+        if s.use_symm and s.topo is None and not self.cast:
+            s.symm.allreduce(lo, n, self.scale, stream=self.side)
+            self.inflight.append((None, view, None))
+            return
+        import torch.distributed as dist
+        ctx = torch.cuda.stream(self.side) if s.cuda else _NullCtx()
+        with ctx:
+            if self.cast:
+                t = self.bf[lo:lo + n]
+                t.copy_(view)
+                w = dist.all_reduce(t, group=s.group, async_op=True)
+            else:
+                t = None
+                w = dist.all_reduce(view, group=s.group, async_op=True)
+        self.inflight.append((w, view, t))
+
+    def finish(self) -> None:
+        """After backward: start what no hook started (parameters without a gradient this step), then make
+        the training stream wait for every bucket; cast back / scale."""
+        s = self.store
+        self._start_ready(force=True)
+        ctx = torch.cuda.stream(self.side) if s.cuda else _NullCtx()
+        with ctx:
+            for w, view, t in self.inflight:
+                if w is None:
+                    continue
+                w.wait()
+                if t is not None:
+                    torch.mul(t, self.scale, out=view)         # bf16 -> fp32 and the 1/nranks scale in one pass
+                else:
+                    view.mul_(self.scale)
+        if s.cuda:
+            torch.cuda.current_stream(s.device).wait_stream(self.side)
+        self.inflight.clear()
+
+
+class _NullCtx:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
 class DenseSync:
     """One object per trainer that applies the configured sync mode around the optimizer step."""
 
@@ -225,6 +343,10 @@ class DenseSync:
         self.async_table = async_table
         self.steps = 0
         self.fold_engine = None
+        self.overlap = None
+        if mode == "allreduce" and FLAGS.pbx_dense_overlap_mb > 0:
+            self.overlap = OverlappedGradReducer(store, int(FLAGS.pbx_dense_overlap_mb * (1 << 20)),
+                                                 FLAGS.pbx_dense_overlap_bf16)
         if mode == "async":
             from ..host import AsyncDenseTable
             self.async_table = async_table or AsyncDenseTable(store.numel, lr=opt.lr)
@@ -237,7 +359,7 @@ class DenseSync:
         plain allreduce mode over symmetric memory with the same ranks as the sparse group."""
         s = self.store
         if (self.mode != "allreduce" or not s.use_symm or s.topo is not None or engine is None
-                or not FLAGS.pbx_fold_dense_allreduce
+                or not FLAGS.pbx_fold_dense_allreduce or self.overlap is not None
                 or getattr(engine, "nranks", 1) != s.nranks):
             return False
         self._fold_desc = (s.symm, 0, s.numel, 1.0 / s.nranks)
@@ -247,6 +369,8 @@ class DenseSync:
         return True
 
     def before_forward(self) -> None:
+        if self.overlap is not None:
+            self.overlap.begin_step()
         if self.fold_engine is not None:
             # several trainers may share one sparse engine (join / update models): the push of THIS
             # step must reduce THIS trainer's gradient buffer
@@ -268,7 +392,9 @@ class DenseSync:
             o.step()
         elif self.mode == "allreduce":
             eng = self.fold_engine
-            if eng is not None and getattr(eng, "fold_done", False):
+            if self.overlap is not None:
+                self.overlap.finish()          # buckets were started from autograd hooks during backward
+            elif eng is not None and getattr(eng, "fold_done", False):
                 eng.fold_done = False          # the sparse push of this step already reduced the grads
             else:
                 s.allreduce_grads()

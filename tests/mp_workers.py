@@ -529,3 +529,58 @@ def cpu_legacy_global_shuffle(rank, world):
     dist.all_reduce(tot)
     return {"before": before, "after": after, "total_before": int(tot[0]), "total_after": int(tot[1]), "owner_ok": ok_owner,
             "sum_signs": int(sum(int(r.u64_signs[0]) for r in ds.records))}
+
+
+def cpu_dense_overlap(rank, world):
+    """Bucketed allreduce started from autograd hooks must give the plain allreduce's parameters (exactly in
+    fp32, closely with the bf16 transport), start buckets DURING backward, and tolerate unused parameters."""
+    from paddlebox_b200.flags import FLAGS, set_flags
+    from paddlebox_b200.parallel.dense import DenseOptimizer, DenseParamStore, DenseSync
+
+    def make():
+        torch.manual_seed(0)
+        return torch.nn.Sequential(torch.nn.Linear(16, 64), torch.nn.ReLU(), torch.nn.Linear(64, 64), torch.nn.ReLU(),
+                                   torch.nn.Linear(64, 32), torch.nn.ReLU(), torch.nn.Linear(32, 1))
+
+    def train(overlap_mb, bf16, steps=4, skip_last=False, kind="adam"):
+        set_flags({"pbx_dense_overlap_mb": overlap_mb, "pbx_dense_overlap_bf16": bf16})
+        model = make()
+        store = DenseParamStore(model, rank, world)
+        sync = DenseSync(store, DenseOptimizer(store, lr=0.05, kind=kind), "allreduce")
+        g = torch.Generator().manual_seed(100 + rank)
+        started = []
+        for _ in range(steps):
+            x = torch.randn(32, 16, generator=g)
+            sync.before_forward()
+            h = model[:-1](x) if skip_last else model(x)         # skip_last: the last layer gets no gradient
+            h.pow(2).mean().backward()
+            if sync.overlap is not None:
+                started.append(sync.overlap.launched_in_backward)
+            sync.after_backward()
+        n_buckets = len(sync.overlap.buckets) if sync.overlap is not None else 0
+        if sync.overlap is not None:
+            sync.overlap.remove()
+        return store.flat.clone(), n_buckets, started
+
+    try:
+        ref, _, _ = train(0.0, False)
+        # 0.004 MB = 4 KB buckets: the 4-layer tower splits into several
+        got, nb, started = train(0.004, False)
+        assert nb >= 3, nb
+        assert torch.equal(ref, got), float((ref - got).abs().max())
+        assert all(s >= nb - 1 for s in started), (started, nb)      # all but (at most) the last bucket under backward
+        # bf16 transport: compared under SGD (Adam's normalisation turns a rounding of a tiny gradient into a full step)
+        ref_sgd, _, _ = train(0.0, False, kind="sgd")
+        got16, _, _ = train(0.004, True, kind="sgd")
+        assert torch.allclose(ref_sgd, got16, atol=2e-3) and not torch.equal(ref_sgd, got16), \
+            float((ref_sgd - got16).abs().max())
+        ref_skip, _, _ = train(0.0, False, skip_last=True)
+        got_skip, _, started = train(0.004, False, skip_last=True)
+        assert torch.equal(ref_skip, got_skip)
+        # replicas stay identical
+        gathered = [torch.zeros_like(got) for _ in range(world)]
+        dist.all_gather(gathered, got)
+        assert all(torch.equal(gathered[0], t) for t in gathered)
+    finally:
+        set_flags({"pbx_dense_overlap_mb": 0.0, "pbx_dense_overlap_bf16": False})
+    return {"buckets": nb, "started": started}

@@ -114,6 +114,11 @@ def test_train_from_dataset_trains_every_local_record_two_ranks(tmp_path):
     assert outs[0]["steps"] == outs[1]["steps"] == 13                               # ceil(200 / 16), equalised
 
 
+def test_overlapped_bucketed_dense_allreduce_two_ranks_gloo():
+    outs = _spawn(W.cpu_dense_overlap, 2, "gloo")
+    assert outs[0]["buckets"] >= 3 and outs[0] == outs[1]
+
+
 def test_legacy_record_global_shuffle_two_ranks_gloo():
     outs = _spawn(W.cpu_legacy_global_shuffle, 2, "gloo")
     assert outs[0]["total_before"] == outs[0]["total_after"] == 110 and all(o["owner_ok"] for o in outs)
