@@ -120,14 +120,35 @@ void KeyAgent::flush_bucket(size_t s, std::vector<uint64_t>& b) {
   b.clear();
 }
 
+// A pass repeats its hot keys thousands of times.  Each adding thread keeps a small direct-mapped table of
+// the keys it has sent recently (256 KB, stays in L2): a key found there is already in its shard's buffer or
+// set and is dropped at once, so only first sightings (and evicted keys) pay for the bucket + shard insert.
+// The table is wiped when the agent's stamp changes: cleared for a new pass, or another agent on this thread.
+static constexpr size_t kRecentSlots = 1 << 15;
+static thread_local std::vector<uint64_t> tl_recent;
+static thread_local uint64_t tl_recent_epoch = 0;
+
 void KeyAgent::add_keys(const uint64_t* keys, size_t n) {
   const size_t S = shards_.size();
+  const bool pow2 = (S & (S - 1)) == 0;
   auto& local = tl_agent_local;
   if (local.size() != S) local.assign(S, {});
+  auto& recent = tl_recent;
+  if (recent.size() != kRecentSlots || tl_recent_epoch != epoch_.load(std::memory_order_relaxed)) {
+    recent.assign(kRecentSlots, 0);
+    tl_recent_epoch = epoch_.load(std::memory_order_relaxed);
+  }
   for (size_t i = 0; i < n; ++i) {
-    const size_t s = (size_t)(mix64(keys[i]) % S);
+    const uint64_t k = keys[i];
+    const uint64_t h = mix64(k);
+    if (k != 0) {
+      uint64_t& slot = recent[(size_t)(h >> 40) & (kRecentSlots - 1)];
+      if (slot == k) continue;
+      slot = k;
+    }
+    const size_t s = pow2 ? (size_t)(h & (S - 1)) : (size_t)(h % S);
     auto& b = local[s];
-    b.push_back(keys[i]);
+    b.push_back(k);
     if (b.size() >= 4096) flush_bucket(s, b);
   }
 }

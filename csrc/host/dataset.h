@@ -79,17 +79,20 @@ struct KeySet {
 // proportional to the unique keys, not to the feasigns read.
 class KeyAgent {
  public:
-  explicit KeyAgent(int shards = 64) : shards_(shards), mu_(shards) {}
+  explicit KeyAgent(int shards = 64) : shards_(shards), mu_(shards), epoch_(next_epoch()) {}
   void add_keys(const uint64_t* keys, size_t n);
   void add_key(uint64_t k) { add_keys(&k, 1); flush_local(); }
   void flush_local();   // publish this thread's buffered keys (call before finalize)
   // every shard's keys sorted (parallel), shards concatenated
   void finalize(ThreadPool* pool, std::vector<uint64_t>* out);
-  void clear() { for (auto& s : shards_) s.clear(); }
+  void clear() { for (auto& s : shards_) s.clear(); epoch_.store(next_epoch()); }
  private:
   void flush_bucket(size_t s, std::vector<uint64_t>& b);
   std::vector<KeySet> shards_;
   std::vector<std::mutex> mu_;
+  // process-wide unique stamp, renewed by clear(): adding threads wipe their recent-key tables when it changes
+  static uint64_t next_epoch() { static std::atomic<uint64_t> g{0}; return ++g; }
+  std::atomic<uint64_t> epoch_;
 };
 
 struct BatchRange { int64_t start; int len; };
