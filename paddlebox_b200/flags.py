@@ -97,6 +97,7 @@ _d("pbx_pass_chunk_rows", 1 << 19, "rows per staging slot of the pass build / wr
 _d("pbx_pass_fetch_threads", 4, "CPU threads fetching host-table rows into pinned staging slots during begin_pass")
 _d("pbx_dense_overlap_mb", 0.0, "> 0: the dense-gradient allreduce runs in buckets of this many MB, each started from an autograd hook as soon as its gradients are final, on a side stream under the rest of backward (large dense models; takes precedence over the fold)")
 _d("pbx_dense_overlap_bf16", False, "overlapped dense allreduce: gradients travel as bf16 (cast before, cast back + scale after)")
+_d("pbx_cpu_emulate_bf16", False, "CPU towers round every GEMM operand to bf16 (fp32 accumulation), the numerics of the GPU towers: for bf16-vs-fp32 training comparisons without a GPU")
 _d("pbx_fold_dense_allreduce", True, "data-parallel dense-gradient allreduce rides on the sparse push kernel's barriers")
 _d("pbx_sparse_dist", False, "GPU worlds: route pull/push through torch.distributed all-to-all (multi-node) instead of the one-node peer-memory engine; CPU worlds with > 1 rank always route this way")
 _d("pbx_sparse_cap_factor", 2.0, "mailbox capacity = factor * max_keys / nranks")

@@ -181,6 +181,24 @@ class _MLPFn(torch.autograd.Function):
         return (dx, None, None) + (None,) * nparam
 
 
+class _EmuBF16Linear(torch.autograd.Function):
+    """CPU statement of the GPU tower's numerics (``FLAGS.pbx_cpu_emulate_bf16``): every GEMM operand —
+    activations, weights, output gradients — rounded to bf16, products accumulated in fp32, master weights
+    and their gradients fp32.  Lets the bf16-vs-fp32 training comparison (AUC parity) run without a GPU."""
+
+    @staticmethod
+    def forward(ctx, x, w, b):
+        xb, wb = x.bfloat16().float(), w.bfloat16().float()
+        ctx.save_for_backward(xb, wb)
+        return xb @ wb.t() + b
+
+    @staticmethod
+    def backward(ctx, g):
+        xb, wb = ctx.saved_tensors
+        gb = g.bfloat16().float()
+        return gb @ wb, gb.t() @ xb, gb.sum(0)
+
+
 class FusedMLP(nn.Module):
     """ReLU tower ``dims[0] -> dims[1] -> ... -> dims[-1]``; the last layer is linear
     unless ``final_relu``.  Parameter names follow the reference's convention
@@ -249,10 +267,12 @@ class FusedMLP(nn.Module):
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         if not x.is_cuda:
+            from ..flags import FLAGS
+            lin = _EmuBF16Linear.apply if FLAGS.pbx_cpu_emulate_bf16 else torch.nn.functional.linear
             h = x
             L = len(self.weights)
             for i, (w, b) in enumerate(zip(self.weights, self.biases)):
-                h = torch.nn.functional.linear(h, w, b)
+                h = lin(h, w, b)
                 if i < L - 1 or self.final_relu:
                     h = torch.relu(h)
             return h

@@ -543,3 +543,50 @@ def test_cpu_training_with_deterministic_merge_flag(tmp_path):
             BoxWrapper.reset_instance()
     a, b = run(False), run(True)
     assert np.allclose(a, b, rtol=1e-4, atol=1e-5) and run(True) == b
+
+
+def test_bf16_tower_numerics_train_to_the_same_auc_as_fp32(tmp_path):
+    """SURVEY 7.3 asks for a check that bf16 towers (fp32 accumulation, fp32 master weights) train like the
+    reference's fp32 towers.  The GPU numerics are stated on the CPU (FLAGS.pbx_cpu_emulate_bf16): same data,
+    same seeds, DeepFM, AUC per pass and final loss must agree closely — and the runs must really differ."""
+    import torch
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    from paddlebox_b200.dataset import DatasetFactory
+    from paddlebox_b200.flags import set_flags
+    from paddlebox_b200.models.ctr import DeepFM
+    from paddlebox_b200.trainer import CTRTrainer, TrainerConfig
+    from tests.util_data import slot_vars, write_files
+    files = write_files(str(tmp_path), n_files=2, lines_per_file=400, n_sparse=8, n_dense=4, key_space=40)
+
+    def run(emulate):
+        set_flags({"pbx_cpu_emulate_bf16": emulate})
+        BoxWrapper.reset_instance()
+        box = BoxWrapper.set_instance(embedx_dim=8, device=torch.device("cpu"), rank=0, world_size=1)
+        box.initialize_gpu_and_load_model({"mf_create_thresholds": 1.0, "learning_rate": 0.1, "mf_learning_rate": 0.1})
+        box.init_metric("AucCalculator", "auc", "label", "pred", metric_phase=1, bucket_size=100000)
+        torch.manual_seed(0)
+        ds = DatasetFactory().create_dataset("PadBoxSlotDataset")
+        ds.set_use_var(slot_vars(8, 4)); ds.set_batch_size(32); ds.set_thread(1); ds.set_filelist(files)
+        model = DeepFM(num_slots=8, embedx_dim=8, dense_dim=4, hidden=(64, 32))
+        tr = CTRTrainer(model, box, TrainerConfig(dense_lr=1e-2))
+        aucs, loss = [], None
+        for _ in range(8):
+            ds.load_into_memory(); ds.begin_pass()
+            st = tr.train_from_dataset(ds)
+            ds.end_pass(False)
+            aucs.append(box.get_metric_msg("auc")[0])
+            loss = st.get("loss", st.get("mean_loss"))
+            ds.release_memory()
+        flat = tr.store.flat.clone()
+        BoxWrapper.reset_instance()
+        return aucs, loss, flat
+
+    try:
+        a32, l32, p32 = run(False)
+        a16, l16, p16 = run(True)
+    finally:
+        set_flags({"pbx_cpu_emulate_bf16": False})
+    assert not torch.equal(p32, p16)                      # the emulation really changed the arithmetic
+    assert a32[-1] > 0.7 and a16[-1] > 0.7
+    assert abs(a32[-1] - a16[-1]) < 0.01, (a32, a16)
+    assert max(abs(x - y) for x, y in zip(a32, a16)) < 0.02, (a32, a16)
