@@ -58,6 +58,16 @@ class PSGPUWrapper(BoxWrapper):
         self._gpu_free.put(None)              # the GPU starts out free
         self.current_task: HeterContext | None = None
         self._running = True
+        # The pre-build thread exchanges keys between ranks while the main thread trains the previous pass and
+        # issues collectives of its own: two threads on one process group would interleave differently on
+        # different ranks.  The build thread gets a group of its own (host arrays: gloo), created here, where
+        # every rank arrives in program order.
+        self._build_group = self.group
+        if self.world_size > 1:
+            import torch.distributed as dist
+            if dist.is_available() and dist.is_initialized():
+                ranks = dist.get_process_group_ranks(self.group) if self.group is not None else None
+                self._build_group = dist.new_group(ranks=ranks, backend="gloo")
         self._build_thread = threading.Thread(target=self._pre_build_loop, name="psgpu-pre-build", daemon=True)
         self._build_thread.start()
 
@@ -92,7 +102,8 @@ class PSGPUWrapper(BoxWrapper):
         keys = sort_unique_u64(np.concatenate([np.zeros(1, np.uint64), raw]))       # key 0 is always registered
         if self.world_size > 1:
             from .parallel.cluster import Cluster
-            mine = Cluster(self.group).all_to_all_arrays(partition_by_owner(keys, self.world_size))
+            mine = Cluster(getattr(self, "_build_group", self.group)).all_to_all_arrays(
+                partition_by_owner(keys, self.world_size))
             keys = sort_unique_u64(np.concatenate(mine)) if mine else np.zeros(0, np.uint64)
         task.keys = keys
         task.timing["pre_build_s"] = time.time() - t0
@@ -148,7 +159,11 @@ class PSGPUWrapper(BoxWrapper):
         if task.error is not None:
             raise task.error
         self._gpu_free.get()                                     # previous pass must have ended
-        self.build_gpu_task(task)
+        try:
+            self.build_gpu_task(task)
+        except BaseException:
+            self._gpu_free.put(None)                             # a failed build must not leave the GPU "taken"
+            raise
         self.current_task = task
         self.timers.add("begin_pass", time.time() - t0)
 

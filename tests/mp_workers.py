@@ -584,3 +584,35 @@ def cpu_dense_overlap(rank, world):
     finally:
         set_flags({"pbx_dense_overlap_mb": 0.0, "pbx_dense_overlap_bf16": False})
     return {"buckets": nb, "started": started}
+
+
+def cpu_psgpu_pipeline_two_ranks(rank, world):
+    """PSGPUWrapper's pre-build thread routes keys between the ranks while the main thread keeps issuing
+    collectives on the world group (what training the previous pass does): the two must not interleave."""
+    from paddlebox_b200.box_wrapper import owner_of
+    from paddlebox_b200.ps_gpu import PSGPUWrapper
+    PSGPUWrapper.reset_instance()
+    box = PSGPUWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=rank, world_size=world)
+    box.init_gpu_ps(conf={"mf_create_thresholds": 0.0})
+    all_keys = [np.arange(1, 400, dtype=np.uint64) * np.uint64(r + 3) for r in range(world)]
+    sizes = []
+    for p in range(3):
+        box.start_build_thread()
+        from paddlebox_b200.ps_gpu import HeterContext
+        task = HeterContext(keys=all_keys[rank] + np.uint64(1000 * p))
+        box._data_ready.put(task)
+        for i in range(25):                                  # "training": collectives on the world group meanwhile
+            t = torch.full((64,), float(rank + i))
+            dist.all_reduce(t)
+            assert float(t[0]) == sum(r + i for r in range(world))
+        box.begin_pass()
+        mine = box._pass_keys
+        assert mine.size and np.all(owner_of(mine, world) == rank)
+        want = np.unique(np.concatenate([k + np.uint64(1000 * p) for k in all_keys] + [np.zeros(1, np.uint64)]))
+        want_mine = want[owner_of(want, world) == rank]
+        assert np.array_equal(mine, want_mine)
+        sizes.append(int(mine.size))
+        box.end_pass()
+    box.finalize()
+    PSGPUWrapper.reset_instance()
+    return sizes

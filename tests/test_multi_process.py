@@ -119,6 +119,11 @@ def test_overlapped_bucketed_dense_allreduce_two_ranks_gloo():
     assert outs[0]["buckets"] >= 3 and outs[0] == outs[1]
 
 
+def test_psgpu_pre_build_thread_has_its_own_group_two_ranks_gloo():
+    outs = _spawn(W.cpu_psgpu_pipeline_two_ranks, 2, "gloo")
+    assert all(len(o) == 3 and min(o) > 0 for o in outs)
+
+
 def test_legacy_record_global_shuffle_two_ranks_gloo():
     outs = _spawn(W.cpu_legacy_global_shuffle, 2, "gloo")
     assert outs[0]["total_before"] == outs[0]["total_after"] == 110 and all(o["owner_ok"] for o in outs)
