@@ -1237,6 +1237,7 @@ int Dataset::load_archive(const std::string& path) {
   const size_t first = records_.size();
   records_.resize(first + (size_t)n, nullptr);
   std::atomic<int64_t> feas{0};
+  std::atomic<bool> corrupt{false};
   ThreadPool pool(std::max(1, merge_thread_num));
   pool.parallel_range((size_t)n, [&](size_t b0, size_t e0, int) {
     int64_t local_feas = 0;
@@ -1256,15 +1257,34 @@ int Dataset::load_archive(const std::string& path) {
       r->f_vals.resize(cnt); if (cnt) memcpy(r->f_vals.data(), q, (size_t)cnt * 4); q += (size_t)cnt * 4;
       memcpy(&no, q, 2); q += 2;
       r->f_offs.resize(no); if (no) memcpy(r->f_offs.data(), q, (size_t)no * 4);
+      records_[first + i] = r;
+      // the length fields were consistent with the file size; the offset tables must also be consistent
+      // with the values they index and with this dataset's slots (a flipped bit in an offset would
+      // otherwise send build_arena / the packers out of bounds)
+      auto offsets_ok = [](const std::vector<uint32_t>& offs, size_t n_vals, int n_slots) {
+        if ((int)offs.size() != n_slots + 1 || offs.front() != 0 || offs.back() != n_vals) return false;
+        for (size_t k = 1; k < offs.size(); ++k) if (offs[k] < offs[k - 1]) return false;
+        return true;
+      };
+      if (!offsets_ok(r->u64_offs, r->u64_vals.size(), n_used_u64_) ||
+          !offsets_ok(r->f_offs, r->f_vals.size(), n_used_f_)) { corrupt.store(true); continue; }
       if (collect_keys) collect_record_keys(r);
       local_feas += (int64_t)r->u64_vals.size();
-      records_[first + i] = r;
     }
     if (collect_keys) agent_.flush_local();
     feas += local_feas;
   });
-  total_feasigns_ += feas.load();
   munmap((void*)base, fsz);
+  if (corrupt.load()) {
+    // refuse the whole file: give its records back and leave the dataset as it was before the call
+    std::vector<SlotRecord*> back(records_.begin() + (long)first, records_.end());
+    back.erase(std::remove(back.begin(), back.end(), nullptr), back.end());
+    records_.resize(first);
+    pool_.put(back);
+    agent_.clear();
+    PBH_REQUIRE(false, "archive %s is damaged (slot offsets do not match its values or this dataset's slots)", path.c_str());
+  }
+  total_feasigns_ += feas.load();
   if (collect_keys) {
     // several archives may be loaded into one pass (global shuffle): keep the union of their keys
     agent_.add_keys(unique_keys_.data(), unique_keys_.size());

@@ -280,6 +280,110 @@ int main(int argc, char** argv) {
     for (int64_t i = 0; i < nn; ++i) CHECK(len[i] >= 1 && len[i] <= 6 && cnt[i] >= 0 && cnt[i] <= 4);
     OK(pbh_graph_destroy(g));
   }
+  // graph store, round-2 surface: weighted edges + weighted sampling, node files with feature slots (well-formed
+  // and damaged), node weights, partitions and their files
+  {
+    void* g = nullptr;
+    OK(pbh_graph_create(&g));
+    std::vector<uint64_t> src, dst;
+    std::vector<float> w;
+    for (int i = 0; i < 8000; ++i) { src.push_back(1 + rnd() % 900); dst.push_back(1 + rnd() % 900); w.push_back((float)(rnd() % 100) / 10.f); }
+    w[3] = 0.f;
+    OK(pbh_graph_add_edges_weighted(g, 0, src.data(), dst.data(), w.data(), (int64_t)src.size(), 1));
+    OK(pbh_graph_build(g, 0));
+    CHECK(pbh_graph_is_weighted(g, 0) == 1);
+    int64_t nn = pbh_graph_num_nodes(g, 0), ne = pbh_graph_num_edges(g, 0);
+    std::vector<uint64_t> ids((size_t)nn), nb((size_t)nn * 5);
+    std::vector<int64_t> rp((size_t)nn + 1), col((size_t)ne);
+    std::vector<int32_t> cnt((size_t)nn);
+    std::vector<float> we((size_t)ne);
+    OK(pbh_graph_export_csr(g, 0, ids.data(), rp.data(), col.data()));
+    OK(pbh_graph_export_weights(g, 0, we.data()));
+    std::vector<std::thread> ths;
+    for (int t = 0; t < 3; ++t)
+      ths.emplace_back([&, t] {
+        std::vector<uint64_t> o((size_t)nn * 5);
+        std::vector<int32_t> c((size_t)nn);
+        pbh_graph_sample_neighbors_weighted(g, 0, ids.data(), nn, 5, 11 + (uint64_t)t, o.data(), c.data());
+      });
+    for (auto& th : ths) th.join();
+    OK(pbh_graph_sample_neighbors_weighted(g, 0, ids.data(), nn, 5, 3, nb.data(), cnt.data()));
+    for (int64_t i = 0; i < nn; ++i) CHECK(cnt[i] >= 0 && cnt[i] <= 5);
+    uint64_t unknown[3] = {0, 999999999ull, ids[0]};
+    int32_t c3[3];
+    uint64_t o3[15];
+    OK(pbh_graph_sample_neighbors_weighted(g, 0, unknown, 3, 5, 1, o3, c3));
+    CHECK(c3[0] == 0 && c3[1] == 0);
+    // weighted edge file and node file, then the same files with bytes knocked out
+    std::string ef = dir + "/edges_w.txt", nf = dir + "/nodes.txt", wf = dir + "/node_w.txt";
+    {
+      FILE* f = fopen(ef.c_str(), "w");
+      for (int i = 0; i < 500; ++i) fprintf(f, "%d\t%d\t%.3f\n", 1 + (int)(rnd() % 90), 1 + (int)(rnd() % 90), (double)(rnd() % 50) / 7.0);
+      fputs("12\t\n\t\t\nnot a number\t4\t1.0\n77 78\n", f);
+      fclose(f);
+      f = fopen(nf.c_str(), "w");
+      for (int i = 1; i <= 90; ++i) fprintf(f, "user\t%d\t1:%d\t2:%d,%d\t7:%d\n", i, i * 3, i + 1000, i + 2000, i % 5);
+      fputs("item\t5\t1:9\nuser\t\nuser\t91\t:\t3:\t:4\tx:y\nuser\t92\t1:18446744073709551615\n", f);
+      fclose(f);
+      f = fopen(wf.c_str(), "w");
+      for (int i = 1; i <= 90; i += 2) fprintf(f, "%d\t%.2f\n", i, i / 10.0);
+      fputs("bad\n93\n\t\n", f);
+      fclose(f);
+    }
+    int64_t nl = 0;
+    OK(pbh_graph_load_weighted_edge_file(g, 1, ef.c_str(), 0, &nl));
+    CHECK(nl >= 500);
+    OK(pbh_graph_build(g, 1));
+    OK(pbh_graph_load_node_file(g, 0, nf.c_str(), "user", ':', &nl));
+    CHECK(nl >= 90);
+    int64_t ntn = pbh_graph_num_typed_nodes(g, 0);
+    std::vector<uint64_t> tn((size_t)ntn);
+    OK(pbh_graph_export_typed_nodes(g, 0, tn.data()));
+    int32_t slots[3] = {1, 2, 9};
+    std::vector<uint64_t> feat((size_t)ntn * 3);
+    OK(pbh_graph_node_features(g, 0, tn.data(), ntn, slots, 3, feat.data()));
+    int64_t nf_ids = 0;
+    OK(pbh_graph_all_feature_ids(g, 0, nullptr, &nf_ids));
+    std::vector<uint64_t> fids((size_t)nf_ids + 1);
+    OK(pbh_graph_all_feature_ids(g, 0, fids.data(), &nf_ids));
+    OK(pbh_graph_load_node_weight(g, 0, wf.c_str(), &nl));
+    std::vector<float> nw((size_t)ntn);
+    OK(pbh_graph_node_weights(g, 0, tn.data(), ntn, nw.data()));
+    for (int round = 0; round < 12; ++round) {
+      std::string bad = dir + "/bad_graph.txt";
+      std::vector<char> bytes;
+      { FILE* f = fopen(round % 2 ? nf.c_str() : ef.c_str(), "rb"); int ch; while ((ch = fgetc(f)) != EOF) bytes.push_back((char)ch); fclose(f); }
+      for (int k = 0; k < 40; ++k) bytes[rnd() % bytes.size()] = (char)(rnd() % 256);
+      bytes.resize(bytes.size() - rnd() % 17);
+      { FILE* f = fopen(bad.c_str(), "wb"); fwrite(bytes.data(), 1, bytes.size(), f); fclose(f); }
+      void* g2 = nullptr;
+      OK(pbh_graph_create(&g2));
+      int64_t n2 = 0;
+      if (round % 2) pbh_graph_load_node_file(g2, 0, bad.c_str(), "user", ':', &n2);
+      else { pbh_graph_load_weighted_edge_file(g2, 0, bad.c_str(), 1, &n2); pbh_graph_build(g2, 0); }
+      OK(pbh_graph_destroy(g2));
+    }
+    // partitions: tiny byte budget -> many parts; shapes, exports and files
+    int nparts = 0;
+    OK(pbh_graph_make_partitions(g, 0, 4096, 2, &nparts));
+    CHECK(nparts >= 2 && pbh_graph_partition_num(g, 0) == nparts);
+    int64_t tot_nodes = 0, tot_edges = 0;
+    for (int p = 0; p < nparts; ++p) {
+      int64_t pn = 0, pe = 0;
+      OK(pbh_graph_partition_shape(g, 0, p, &pn, &pe));
+      std::vector<uint64_t> pid((size_t)pn), pcol((size_t)pe);
+      std::vector<int64_t> prp((size_t)pn + 1);
+      std::vector<float> pw((size_t)pe);
+      OK(pbh_graph_export_partition(g, 0, p, pid.data(), prp.data(), pcol.data(), pw.data()));
+      CHECK(prp[(size_t)pn] == pe);
+      tot_nodes += pn; tot_edges += pe;
+    }
+    CHECK(tot_nodes == nn && tot_edges == ne);
+    for (int i = 0; i < nparts + 2; ++i) pbh_graph_next_partition(g, 0);
+    OK(pbh_graph_export_partition_files(g, 0, dir.c_str()));
+    CHECK(pbh_graph_partition_shape(g, 0, nparts + 5, &tot_nodes, &tot_edges) != 0);
+    OK(pbh_graph_destroy(g));
+  }
   // metrics: concurrent adds, WuAUC, state export / import
   {
     void* a = nullptr;

@@ -567,6 +567,7 @@ def test_bf16_tower_numerics_train_to_the_same_auc_as_fp32(tmp_path):
         torch.manual_seed(0)
         ds = DatasetFactory().create_dataset("PadBoxSlotDataset")
         ds.set_use_var(slot_vars(8, 4)); ds.set_batch_size(32); ds.set_thread(1); ds.set_filelist(files)
+        ds.set_merge_thread_num(1)                      # one reader, one merger: the record order is the file order
         model = DeepFM(num_slots=8, embedx_dim=8, dense_dim=4, hidden=(64, 32))
         tr = CTRTrainer(model, box, TrainerConfig(dense_lr=1e-2))
         aucs, loss = [], None
