@@ -489,7 +489,7 @@ class HostTable {
   // mode 0 = all (batch model, full state), 1 = delta (dirty rows, serving format),
   //      2 = base (serving format: no optimizer state), 3 = batch model
   int save(const std::string& dir, int mode, int part_shard_base, float base_threshold, float delta_threshold,
-           int64_t* n_saved, bool clear_dirty) {
+           int64_t* n_saved, int clear_dirty) {
     int64_t total = 0;
     for (size_t si = 0; si < shards_.size(); ++si) {
       Shard& s = shards_[si];
@@ -529,7 +529,9 @@ class HostTable {
         }
         fputc('\n', fp);
         ++total;
-        if (clear_dirty && mode == 1 && in_mem) s.dirty[i] = 0;
+        // clear_dirty: 1 = a delta save clears the flags of the rows it wrote; 2 = so does a full save (mode 0
+        // writes every row: the delta baseline is reset as a whole, what a base save wants)
+        if (in_mem && ((clear_dirty && mode == 1) || (clear_dirty == 2 && mode == 0))) s.dirty[i] = 0;
       }
       fclose(fp);
     }
@@ -699,7 +701,7 @@ int64_t pbh_table_shrink(void* h, float decay, float delete_threshold, float del
 int pbh_table_save(void* h, const char* dir, int mode, int part_shard_base, float base_threshold,
                    float delta_threshold, int clear_dirty, int64_t* n_saved) {
   return ((HostTable*)h)->save(dir, mode, part_shard_base, base_threshold, delta_threshold, n_saved,
-                               clear_dirty != 0);
+                               clear_dirty);
 }
 int pbh_table_load_file(void* h, const char* path, int serving, int64_t* n_loaded) {
   return ((HostTable*)h)->load_file(path, serving != 0, n_loaded);

@@ -336,17 +336,14 @@ class BoxWrapper:
         """Full training checkpoint ("batch model", every optimizer state) + serving base
         ("xbox model")  (box_wrapper.cc:1286-1305)."""
         self._sync_to_host()
-        n1 = self.host_table.save(batch_model_path, mode=0, shard_base=self.rank, clear_dirty=False)
-        msg = f"batch_model={n1}"
+        msg_x = ""
         if xbox_model_path:
             n2 = self.host_table.save(xbox_model_path, mode=2, shard_base=self.rank, clear_dirty=False)
-            msg += f" xbox_base={n2}"
-        # a base save resets the delta baseline
-        self.host_table.save(os.path.join(batch_model_path, ".delta_reset"), mode=1, shard_base=self.rank,
-                             clear_dirty=True)
-        import shutil
-        shutil.rmtree(os.path.join(batch_model_path, ".delta_reset"), ignore_errors=True)
-        return msg
+            msg_x = f" xbox_base={n2}"
+        # the full save goes last and resets the delta baseline (every row is written, every dirty flag cleared);
+        # no scratch files: several ranks save into one directory at the same time
+        n1 = self.host_table.save(batch_model_path, mode=0, shard_base=self.rank, clear_dirty=2)
+        return f"batch_model={n1}" + msg_x
 
     def save_delta(self, xbox_model_path: str) -> str:
         """Serving-format delta of the keys touched since the last save (box_wrapper.cc:1306-1315)."""

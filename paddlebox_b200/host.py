@@ -112,7 +112,9 @@ class HostTable:
                                          C.c_float(delete_after_unseen_days))
 
     def save(self, directory: str, mode: int = 0, shard_base: int = 0, base_threshold: float = 0.0,
-             delta_threshold: float = 0.0, clear_dirty: bool = True) -> int:
+             delta_threshold: float = 0.0, clear_dirty: "bool | int" = True) -> int:
+        """``clear_dirty``: True / 1 = a delta save (mode 1) clears the dirty flags of the rows it wrote;
+        2 = a full save (mode 0) clears them too (the delta baseline is reset, as after ``save_base``)."""
         os.makedirs(directory, exist_ok=True)
         n = C.c_int64()
         N.hcheck(N.host().pbh_table_save(self._h, directory.encode(), mode, shard_base, C.c_float(base_threshold),
