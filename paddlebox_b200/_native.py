@@ -94,6 +94,11 @@ class NativeError(RuntimeError):
 
 
 def _lib_path(name: str) -> Path:
+    # PBX_HOST_LIB / PBX_CUDA_LIB: load another build of a library (a sanitizer build of the host runtime,
+    # benchmarks/sanitize_pytests.sh)
+    override = os.environ.get(f"{name.upper()}_LIB")
+    if override:
+        return Path(override)
     return _build.LIB_DIR / f"lib{name}.so"
 
 

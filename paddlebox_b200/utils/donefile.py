@@ -32,7 +32,7 @@ class ModelManifest:
         # keep the complete, parsable lines only: a torn tail left by a crashed writer must not swallow the
         # new entry
         old = "".join(json.dumps(e, sort_keys=True) + "\n" for e in self._read(name))
-        tmp = path + ".tmp"
+        tmp = f"{path}.tmp.{os.getpid()}"          # (one writer per manifest by convention: rank 0 of the job)
         with open(tmp, "w") as f:
             f.write(old + json.dumps(entry, sort_keys=True) + "\n")
             f.flush()
