@@ -1,0 +1,90 @@
+"""Static checks of the Python layer.  Its CUDA-only branches never execute on a CPU box, so two classes of
+mistakes that only a GPU run would show are caught here instead: a name that is bound nowhere, and a call
+into a native library of an entry point that library does not export."""
+import os
+import re
+import subprocess
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_no_undefined_names_in_the_python_layer():
+    sys.path.insert(0, os.path.join(ROOT, "benchmarks"))
+    import undefined_names
+    problems = []
+    for top in ("paddlebox_b200", "bench.py", "baseline", "benchmarks", "examples", "__graft_entry__.py", "tests"):
+        p = os.path.join(ROOT, top)
+        files = [p] if p.endswith(".py") else [os.path.join(d, f) for d, _, fs in os.walk(p) for f in fs
+                                               if f.endswith(".py") and "_ref" not in d]
+        for f in files:
+            problems += undefined_names.check(f)
+    assert not problems, "\n".join(problems)
+
+
+def _exports(lib):
+    out = subprocess.run(["nm", "-D", "--defined-only", lib], capture_output=True, text=True, check=True).stdout
+    return {ln.split()[-1] for ln in out.splitlines() if ln.strip()}
+
+
+def test_every_native_entry_point_called_from_python_is_exported():
+    from paddlebox_b200 import _build
+    libs = _build.build_all(force=False, verbose=False)
+    exported = set()
+    for lib in libs.values():
+        exported |= _exports(str(lib))
+    if "cuda" not in libs:
+        import pytest
+        pytest.skip("no nvcc: libpbx_cuda.so not built here")
+    called = {}
+    pat = re.compile(r"\.\s*(pb[xh]_[a-z0-9_]+)\s*\(")
+    for d, _, fs in os.walk(os.path.join(ROOT, "paddlebox_b200")):
+        for f in fs:
+            if f.endswith(".py"):
+                src = open(os.path.join(d, f)).read()
+                for m in pat.finditer(src):
+                    called.setdefault(m.group(1), f)
+    for extra in ("bench.py",):
+        for m in pat.finditer(open(os.path.join(ROOT, extra)).read()):
+            called.setdefault(m.group(1), extra)
+    assert len(called) > 80                                   # the pattern really finds the call sites
+    missing = {n: f for n, f in called.items() if n not in exported}
+    assert not missing, f"called from Python but not exported by libpbx_cuda.so / libpbx_host.so: {missing}"
+
+
+def _prototypes():
+    """name -> parameter count, from the two C headers."""
+    protos = {}
+    for h in ("include/pbx_cuda.h", "include/pbx_host.h"):
+        src = open(os.path.join(ROOT, h)).read()
+        src = re.sub(r"/\*.*?\*/", " ", src, flags=re.S)
+        src = re.sub(r"//[^\n]*", " ", src)
+        for m in re.finditer(r"\b(pb[xh]_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", src, flags=re.S):
+            args = m.group(2).strip()
+            n = 0 if args in ("", "void") else args.count(",") + 1
+            protos[m.group(1)] = n
+    return protos
+
+
+def test_native_calls_pass_as_many_arguments_as_the_prototype_declares():
+    """ctypes does not check the argument count of a foreign call: one argument short and the callee reads
+    garbage.  Every ``lib.pbx_*(...)`` / ``lib.pbh_*(...)`` call in the package is compared with the header."""
+    import ast
+    protos = _prototypes()
+    assert len(protos) > 150
+    bad, seen = [], 0
+    files = [os.path.join(d, f) for d, _, fs in os.walk(os.path.join(ROOT, "paddlebox_b200")) for f in fs
+             if f.endswith(".py")] + [os.path.join(ROOT, "bench.py")]
+    for path in files:
+        tree = ast.parse(open(path).read(), path)
+        for node in ast.walk(tree):
+            if isinstance(node, ast.Call) and isinstance(node.func, ast.Attribute) and \
+                    re.fullmatch(r"pb[xh]_[a-z0-9_]+", node.func.attr) and node.func.attr in protos:
+                if any(isinstance(a, ast.Starred) for a in node.args) or node.keywords:
+                    continue
+                seen += 1
+                if len(node.args) != protos[node.func.attr]:
+                    bad.append(f"{os.path.relpath(path, ROOT)}:{node.lineno}: {node.func.attr} called with "
+                               f"{len(node.args)} arguments, declared with {protos[node.func.attr]}")
+    assert seen > 150, seen
+    assert not bad, "\n".join(bad)
