@@ -88,3 +88,41 @@ def test_native_calls_pass_as_many_arguments_as_the_prototype_declares():
                                f"{len(node.args)} arguments, declared with {protos[node.func.attr]}")
     assert seen > 150, seen
     assert not bad, "\n".join(bad)
+
+
+def test_float_and_64_bit_scalars_are_wrapped_for_ctypes():
+    """No ``argtypes`` are declared, so ctypes converts a bare Python int to a 32-bit C int and refuses a bare
+    Python float: every ``float`` / ``double`` / 64-bit scalar parameter must be passed through ``C.c_*``."""
+    import ast
+    params = {}
+    for h in ("include/pbx_cuda.h", "include/pbx_host.h"):
+        src = open(os.path.join(ROOT, h)).read()
+        src = re.sub(r"/\*.*?\*/", " ", src, flags=re.S)
+        src = re.sub(r"//[^\n]*", " ", src)
+        for m in re.finditer(r"\b(pb[xh]_[a-z0-9_]+)\s*\(([^;{]*?)\)\s*;", src, flags=re.S):
+            a = m.group(2).strip()
+            params[m.group(1)] = [] if a in ("", "void") else [x.strip() for x in a.split(",")]
+    bad, seen = [], 0
+    files = [os.path.join(d, f) for d, _, fs in os.walk(os.path.join(ROOT, "paddlebox_b200")) for f in fs
+             if f.endswith(".py")] + [os.path.join(ROOT, "bench.py")]
+    for path in files:
+        for node in ast.walk(ast.parse(open(path).read(), path)):
+            if not (isinstance(node, ast.Call) and isinstance(node.func, ast.Attribute) and node.func.attr in params):
+                continue
+            ps = params[node.func.attr]
+            if len(ps) != len(node.args):
+                continue
+            for p, a in zip(ps, node.args):
+                if "*" in p:
+                    continue
+                src = ast.unparse(a)
+                if re.search(r"\b(float|double)\b", p):
+                    seen += 1
+                    if not re.match(r"C\.c_(float|double)\(", src):
+                        bad.append(f"{os.path.relpath(path, ROOT)}:{node.lineno}: {node.func.attr}({p}) <- {src}")
+                elif re.search(r"\b(u?int64_t|size_t|long long)\b", p):
+                    seen += 1
+                    if not re.match(r"C\.c_(u?int64|size_t|u?longlong)\(", src):
+                        bad.append(f"{os.path.relpath(path, ROOT)}:{node.lineno}: {node.func.attr}({p}) <- {src}")
+    assert seen > 100, seen
+    assert not bad, "\n".join(bad)
