@@ -182,6 +182,30 @@ int pbh_dataset_set_input_index(void* h, void* index) {
   d->input_index = index;           // the plugin's offset callback is bound when loading starts
   return 0;
 }
+// the feed configuration of `src` (slots, parser, threads, flags, plugin, omitted slots, reader cores) onto `dst`;
+// the file list and the rank / world of the file dealing stay dst's own (streaming readers deal files themselves)
+int pbh_dataset_copy_config(void* dst_h, void* src_h) {
+  Dataset* d = (Dataset*)dst_h;
+  const Dataset* s = (const Dataset*)src_h;
+  d->slots = s->slots;
+  d->pipe_command = s->pipe_command;
+  d->parser_plugin = s->parser_plugin;
+  d->thread_num = s->thread_num;
+  d->merge_thread_num = s->merge_thread_num;
+  d->batch_size = s->batch_size;
+  d->parse_ins_id = s->parse_ins_id;
+  d->parse_logkey = s->parse_logkey;
+  d->sample_rate = s->sample_rate;
+  d->enable_pv_merge = s->enable_pv_merge;
+  d->collect_keys = s->collect_keys;
+  d->compact_batches = s->compact_batches;
+  d->compact_limit_mb = s->compact_limit_mb;
+  d->input_index = s->input_index;
+  d->reader_cores = s->reader_cores;
+  d->omit_slots = s->omit_slots;
+  d->parser_file_mode = s->parser_file_mode;
+  return d->slots.empty() ? 0 : d->finalize_slots();
+}
 int pbh_dataset_load_into_memory(void* h) { return ((Dataset*)h)->load_into_memory(); }
 int pbh_dataset_preload_into_memory(void* h) { return ((Dataset*)h)->preload_into_memory(); }
 int pbh_dataset_wait_preload_done(void* h) { return ((Dataset*)h)->wait_preload_done(); }

@@ -174,6 +174,8 @@ int pbh_dataset_set_reader_cores(void* ds, const int* cores, int n);
 /* slots (indices in set_slots order) whose feasigns are not PS keys: skipped by the key collection
  * (slot_omit_in_feedpass of InitializeGPUAndLoadModel, data_feed.cc:3119-3146) */
 int pbh_dataset_set_omit_slots(void* ds, const int* slot_indices, int n);
+/* feed configuration of src onto dst (not the file list, not rank / world): streaming readers keep several handles */
+int pbh_dataset_copy_config(void* dst, void* src);
 /* SSD tier (closed-library LoadSSD2Mem / CheckNeedLimitMem, fleet/box_wrapper.cc:1316-1324): cold rows
  * move to one append-only file per shard under `dir`; a lookup that misses host memory promotes the
  * row back.  spill: rows unseen for >= min_unseen_days (negative: ignore age), then — if

@@ -526,12 +526,23 @@ class InMemoryDataset(DatasetBase):
 
 
 class QueueDataset(InMemoryDataset):
-    """Streaming flavour (reference ``QueueDataset``: no shuffle).  Here it loads file by file
-    and never shuffles or collects keys."""
+    """Streaming dataset (reference ``QueueDataset``, python/paddle/fluid/dataset.py:1106-1230; each DataFeed reads
+    its share of the files and hands batches to its worker as it goes — nothing is held for a whole pass, nothing
+    is shuffled, no pass keys are collected).
+
+    ``batches()`` without a previous ``load_into_memory()`` streams: this rank's files (``filelist[rank::world]``)
+    are read ``thread_num`` at a time; while the batches of one group are being consumed, a background thread
+    parses the next group into a second native handle, so host memory holds two groups of files at most and the
+    reader never waits for a whole pass.  Batches do not span groups (the last batch of a group may be short).
+    ``load_into_memory()`` is still accepted (compatibility): the dataset then behaves like an unshuffled
+    in-memory dataset."""
+
+    streaming = True
 
     def __init__(self):
         super().__init__()
         self._native.set("collect_keys", 0)
+        self._stream_handles = None
 
     def local_shuffle(self):
         raise NotImplementedError("QueueDataset does not support local shuffle")
@@ -541,6 +552,73 @@ class QueueDataset(InMemoryDataset):
 
     def prepare_train(self, num_workers=1, worker=0, shuffle=None, min_batches=0):
         super().prepare_train(num_workers, worker, False, min_batches)
+
+    def is_loaded(self) -> bool:
+        return self._native.num_records() > 0 or self._prepared_workers > 0
+
+    def file_groups(self) -> list:
+        mine = self.filelist[self._rank::max(1, self._world)]
+        g = max(1, int(self.thread_num))
+        return [mine[i:i + g] for i in range(0, len(mine), g)]
+
+    def batches(self, worker: int | None = None, device: torch.device | None = None, prefetch: int = 2,
+                with_ins_id: bool = False) -> Iterator[SlotBatch]:
+        if self.is_loaded():
+            return super().batches(worker, device, prefetch, with_ins_id)
+        return self._stream(device or self._device, prefetch, with_ins_id, host=False)
+
+    def host_batches(self, worker: int | None = None, prefetch: int = 4, with_ins_id: bool = False):
+        if self.is_loaded():
+            return super().host_batches(worker, prefetch, with_ins_id)
+        return self._stream(torch.device("cuda"), prefetch, with_ins_id, host=True)
+
+    def _stream(self, device, prefetch: int, with_ins_id: bool, host: bool):
+        import threading
+        from .host import NativeDataset
+        groups = self.file_groups()
+        if self._stream_handles is None:
+            self._stream_handles = [NativeDataset(), NativeDataset()]
+        handles = self._stream_handles
+        for h in handles:
+            h.copy_config_from(self._native)       # rank / world stay (0, 1): the groups are already this rank's
+            h.set("collect_keys", 0)
+        self.stream_stats = {"groups": len(groups), "records": 0, "max_resident_records": 0}
+
+        def load(h, files):
+            h.release_memory()
+            h.set_filelist(files)
+            h.load_into_memory()
+            h.prepare_train(1, False, 0, 0)
+
+        err: list = []
+
+        def load_bg(h, files):
+            try:
+                load(h, files)
+            except BaseException as e:  # noqa: BLE001  (re-raised in the consumer)
+                err.append(e)
+
+        if not groups:
+            return
+        load(handles[0], groups[0])
+        for gi in range(len(groups)):
+            cur = handles[gi % 2]
+            th = None
+            if gi + 1 < len(groups):
+                th = threading.Thread(target=load_bg, args=(handles[(gi + 1) % 2], groups[gi + 1]), daemon=True)
+                th.start()
+            n_cur = cur.num_records()
+            self.stream_stats["records"] += n_cur
+            loader = _BatchLoader(cur, 0, device, prefetch, with_ins_id, self._want_meta(), getattr(self, "max_rank", 3))
+            yield from (loader.host_batches() if host else iter(loader))
+            if th is not None:
+                th.join()
+                if err:
+                    raise err[0]
+                self.stream_stats["max_resident_records"] = max(self.stream_stats["max_resident_records"],
+                                                                n_cur + handles[(gi + 1) % 2].num_records())
+            cur.release_memory()
+        self.stream_stats["max_resident_records"] = max(self.stream_stats["max_resident_records"], n_cur)
 
 
 class BoxPSDataset(InMemoryDataset):

@@ -333,6 +333,10 @@ class NativeDataset:
         arr = (C.c_int * len(slot_indices))(*slot_indices)
         N.hcheck(N.host().pbh_dataset_set_omit_slots(self._h, arr, len(slot_indices)))
 
+    def copy_config_from(self, other: "NativeDataset") -> None:
+        """Everything but the file list and the rank / world of the file dealing."""
+        N.hcheck(N.host().pbh_dataset_copy_config(self._h, other._h))
+
     def set_input_index(self, index_handle):
         """Attach an ``InputTable`` key index (parse-time ``GetOffsetFunc`` for parser plugins)."""
         N.hcheck(N.host().pbh_dataset_set_input_index(self._h, index_handle))

@@ -312,13 +312,34 @@ class CTRTrainer:
                 raise RuntimeError(f"rank {self.rank}: cannot split {local} batches into {most} (too few records)")
         return 0
 
+    def _stream_batches(self, dataset, want_ids: bool):
+        """Batches of a streaming dataset.  One rank: as they come.  Several ranks: nobody knows its batch count
+        in advance, yet every rank must take the same number of steps (pull / push meet at in-kernel barriers,
+        the dense sync is a collective), so the ranks agree before every step that all of them still have a
+        batch; the pass ends for everyone when the first rank runs dry (the reference leaves equal shares to
+        the user: a QueueDataset job with unequal file shares hangs in its first collective)."""
+        it = iter(dataset.batches(with_ins_id=want_ids))
+        if self.world == 1:
+            yield from it
+            return
+        from .parallel.cluster import OP_MIN, Cluster
+        while True:
+            b = next(it, None)
+            if not Cluster.ins().allreduce(int(b is not None), OP_MIN):
+                return
+            yield b
+
     def train_from_dataset(self, dataset, print_period: int = 0, fetch_handler=None) -> dict:
         """Train every batch the dataset dealt to this worker; returns pass statistics."""
-        worker = self._deal_batches(dataset)
         t0 = time.time()
         n_ins, losses = 0, []
         want_ids = self.dumper is not None and bool(self.cfg.dump_fields)
-        for i, batch in enumerate(dataset.batches(worker=worker, with_ins_id=want_ids)):
+        if getattr(dataset, "streaming", False) and not dataset.is_loaded():
+            batches = self._stream_batches(dataset, want_ids)      # QueueDataset: nothing is loaded up front
+        else:
+            worker = self._deal_batches(dataset)
+            batches = dataset.batches(worker=worker, with_ins_id=want_ids)
+        for i, batch in enumerate(batches):
             loss = self.train_step(batch)
             n_ins += batch.batch_size
             if print_period and (i + 1) % print_period == 0:

@@ -616,3 +616,32 @@ def cpu_psgpu_pipeline_two_ranks(rank, world):
     box.finalize()
     PSGPUWrapper.reset_instance()
     return sizes
+
+
+def cpu_queue_dataset_streaming_two_ranks(rank, world, data_dir):
+    """Streaming dataset on two ranks with unequal file shares: both take the same number of steps (the pass
+    ends for everyone when the first rank runs dry) and the sharded sparse path does not hang."""
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    from paddlebox_b200.dataset import DatasetFactory
+    from paddlebox_b200.models.ctr import CtrDnn
+    from paddlebox_b200.trainer import CTRTrainer, TrainerConfig
+    from tests.util_data import slot_vars
+    files = sorted(os.path.join(data_dir, f) for f in os.listdir(data_dir) if f.startswith("part-"))
+    box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=rank, world_size=world)
+    box.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0})
+    ds = DatasetFactory().create_dataset("QueueDataset")
+    ds.set_use_var(slot_vars(3, 2)); ds.set_batch_size(10); ds.set_thread(1)
+    ds.set_filelist(files)
+    ds.set_rank_world(rank, world)
+    assert len(ds.file_groups()) == (3 if rank == 0 else 2)
+    torch.manual_seed(0)
+    tr = CTRTrainer(CtrDnn(num_slots=3, embedx_dim=4, dense_dim=2, hidden=(8,)), box, TrainerConfig())
+    box.begin_pass()
+    st = tr.train_from_dataset(ds)
+    box.end_pass()
+    flat = tr.store.flat.clone()
+    gathered = [torch.zeros_like(flat) for _ in range(world)]
+    dist.all_gather(gathered, flat)
+    assert all(torch.allclose(gathered[0], t) for t in gathered)      # dense replicas stayed in step
+    BoxWrapper.reset_instance()
+    return {"steps": st["steps"], "instances": st["instances"]}

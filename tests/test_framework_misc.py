@@ -591,3 +591,49 @@ def test_bf16_tower_numerics_train_to_the_same_auc_as_fp32(tmp_path):
     assert a32[-1] > 0.7 and a16[-1] > 0.7
     assert abs(a32[-1] - a16[-1]) < 0.01, (a32, a16)
     assert max(abs(x - y) for x, y in zip(a32, a16)) < 0.02, (a32, a16)
+
+
+def test_queue_dataset_streams_without_loading_the_pass(tmp_path):
+    """No load_into_memory: files are read a group at a time while the previous group's batches are consumed;
+    every line arrives exactly once, in file order with one reader, and at most two groups are resident."""
+    import torch
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    from paddlebox_b200.dataset import DatasetFactory
+    from paddlebox_b200.models.ctr import CtrDnn
+    from paddlebox_b200.trainer import CTRTrainer, TrainerConfig
+    from tests.util_data import slot_vars, write_files
+    files = write_files(str(tmp_path), n_files=5, lines_per_file=37, n_sparse=3, n_dense=2, key_space=50)
+    ds = DatasetFactory().create_dataset("QueueDataset")
+    ds.set_use_var(slot_vars(3, 2)); ds.set_batch_size(8); ds.set_thread(1); ds.set_merge_thread_num(1)
+    ds.set_filelist(files)
+    assert not ds.is_loaded() and ds.file_groups() == [[f] for f in files]
+    labels = torch.cat([b.dense[:, 0] for b in ds.batches(device=torch.device("cpu"))])
+    want = [float(line.split()[1]) for f in files for line in open(f)]
+    assert labels.tolist() == want                                   # every line once, in file order
+    assert ds.stream_stats["records"] == 5 * 37 and ds.stream_stats["groups"] == 5
+    assert ds.stream_stats["max_resident_records"] <= 2 * 37          # two groups at most, never the pass
+    assert ds.get_memory_data_size() == 0                             # the dataset itself holds nothing
+    # several files per group with several readers: nothing lost, nothing doubled
+    ds.set_thread(2)
+    assert [len(g) for g in ds.file_groups()] == [2, 2, 1]
+    n = sum(b.batch_size for b in ds.batches(device=torch.device("cpu")))
+    assert n == 5 * 37
+    # a bad file in a later group surfaces as an error in the consumer, not as a silent short pass
+    ds.set_filelist(files[:2] + [str(tmp_path / "missing")])
+    ds.set_thread(1)
+    with pytest.raises(Exception):
+        for _ in ds.batches(device=torch.device("cpu")):
+            pass
+    # and it trains through the public entry point without a feed pass: keys are created on first sight
+    ds.set_filelist(files)
+    BoxWrapper.reset_instance()
+    try:
+        box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=0, world_size=1)
+        box.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0})
+        tr = CTRTrainer(CtrDnn(num_slots=3, embedx_dim=4, dense_dim=2, hidden=(8,)), box, TrainerConfig())
+        box.begin_pass()
+        st = tr.train_from_dataset(ds)
+        box.end_pass()
+        assert st["instances"] == 5 * 37 and st["steps"] >= 5 * 5
+    finally:
+        BoxWrapper.reset_instance()

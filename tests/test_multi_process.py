@@ -124,6 +124,14 @@ def test_psgpu_pre_build_thread_has_its_own_group_two_ranks_gloo():
     assert all(len(o) == 3 and min(o) > 0 for o in outs)
 
 
+def test_queue_dataset_streams_on_two_ranks_with_unequal_shares(tmp_path):
+    from tests.util_data import write_files
+    write_files(str(tmp_path), n_files=5, lines_per_file=40, n_sparse=3, n_dense=2, key_space=60)
+    outs = _spawn(W.cpu_queue_dataset_streaming_two_ranks, 2, "gloo", args=(str(tmp_path),))
+    # rank 1 has two files of 40 lines = 8 batches of 10: both ranks stop there
+    assert outs[0]["steps"] == outs[1]["steps"] == 8 and outs[1]["instances"] == 80
+
+
 def test_legacy_record_global_shuffle_two_ranks_gloo():
     outs = _spawn(W.cpu_legacy_global_shuffle, 2, "gloo")
     assert outs[0]["total_before"] == outs[0]["total_after"] == 110 and all(o["owner_ok"] for o in outs)
