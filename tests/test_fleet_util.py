@@ -1,0 +1,160 @@
+"""FleetUtil / GPUPSUtil: the job-script layer around the wrapper (reference fleet_util.py)."""
+import json
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from paddlebox_b200 import fleet_util as FU
+from paddlebox_b200.box_wrapper import BoxWrapper
+
+
+def test_brace_expansion_and_online_pass_interval():
+    assert FU.expand_braces("{20190720..20190722}") == ["20190720", "20190721", "20190722"]
+    assert FU.expand_braces("{0..3}") == ["0", "1", "2", "3"] and FU.expand_braces("{08..10}") == ["08", "09", "10"]
+    assert FU.expand_braces("{a,b}") == ["a", "b"] and FU.expand_braces("7") == ["7"]
+    u = FU.FleetUtil()
+    # the reference's docstring example: 5-minute splits, 2 per pass -> 144 passes of 2 splits
+    iv = u.get_online_pass_interval("{20190720..20190729}", "{0..23}", 5, 2, False)
+    assert len(iv) == 144 and iv[0] == ["0000", "0005"] and iv[1] == ["0010", "0015"] and iv[-1] == ["2350", "2355"]
+    hourly = u.get_online_pass_interval("{20190720..20190720}", "{0..23}", 60, 1, True)
+    assert hourly == [["%02d" % h] for h in range(24)]
+    part = u.get_online_pass_interval("x", "{8..9}", 30, 2, False)
+    assert part == [["0800", "0830"], ["0900", "0930"]]
+
+
+def test_metrics_from_raw_statistics_match_the_host_calculator():
+    from paddlebox_b200.host import HostAuc
+    rng = np.random.default_rng(0)
+    n, nb = 20000, 1000
+    p = rng.random(n).astype(np.float32) ** 2
+    y = (rng.random(n) < p).astype(np.float32)
+    calc = HostAuc(nb)
+    calc.add(p, y)
+    want = calc.compute()                      # [auc, bucket_error, mae, rmse, actual, predicted, copc, size]
+    idx = np.minimum((p.astype(np.float64) * nb).astype(np.int64), nb - 1)
+    pos = np.bincount(idx, weights=y, minlength=nb)
+    neg = np.bincount(idx, weights=1 - y, minlength=nb)
+    d = p.astype(np.float64) - y
+    got = FU.FleetUtil.metrics_from_stats(pos, neg, float((d * d).sum()), float(np.abs(d).sum()), float(p.sum()),
+                                          float(p.sum()), float(y.sum()), float(n))
+    assert got[8] == n and abs(got[0] - want[0]) < 1e-9 and abs(got[1] - want[1]) < 1e-9
+    assert np.allclose(got[2:7], want[2:7], rtol=1e-5)
+    assert FU.auc_from_buckets(np.zeros(8), np.ones(8)) == 0.5          # one class absent
+    assert FU.FleetUtil.metrics_from_stats(pos * 0, neg * 0, 0, 0, 0, 0, 0, 0)[0] == 0.5
+
+
+@pytest.fixture
+def box():
+    BoxWrapper.reset_instance()
+    b = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=0, world_size=1)
+    b.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0})
+    yield b
+    BoxWrapper.reset_instance()
+
+
+def _touch(box, keys, clicks=1.0):
+    k = np.asarray(keys, dtype=np.uint64)
+    box.host_table.fetch_rows(k, create=True)
+    push = np.zeros((k.size, box.host_table.layout.push_stride), np.float32)
+    push[:, 1] = 3.0
+    push[:, 2] = clicks
+    push[:, 3:] = 0.05
+    box.host_table.push(k, torch.from_numpy(push))
+
+
+def test_a_training_day_through_fleet_util(tmp_path, box):
+    out = str(tmp_path / "output")
+    u = FU.FleetUtil(box=box)
+    assert u.get_last_save_model(out)[:3] == [-1, -1, ""] and u.get_last_save_xbox_base(out)[:2] == [-1, -1]
+    key = 1563000000
+    _touch(box, range(1, 101))
+    # pass 1: delta + patch donefile
+    assert u.save_delta_model(out, 20190722, 1) == 100
+    assert os.path.isdir(f"{out}/20190722/delta-1")
+    assert u.write_xbox_donefile(out, 20190722, 1, key, ["/data/a", "/data/b"], hadoop_fs_name="hdfs://ns")
+    assert not u.write_xbox_donefile(out, 20190722, 1, key, "/data/a")          # not newer: refused
+    _touch(box, range(50, 121))
+    assert u.save_delta_model(out, 20190722, 2) == 71                            # only what changed since pass 1
+    assert u.write_xbox_donefile(out, 20190722, 2, key, "/data/c", hadoop_fs_name="hdfs://ns")
+    lines = open(f"{out}/xbox_patch_done.txt").read().strip().split("\n")
+    assert len(lines) == 2
+    e = json.loads(lines[0])
+    assert list(e) == ["id", "key", "input", "record_count", "partition_type", "job_name", "ins_tag", "ins_path",
+                       "job_id", "monitor_data", "monitor_path", "mpi_size"]
+    assert e["input"] == f"hdfs://ns{out}/20190722/delta-1/000" and e["key"] == str(key) and e["ins_path"] == "/data/a,/data/b"
+    assert e["record_count"] == "111111" and e["partition_type"] == "2" and e["mpi_size"] == "1"
+    assert u.get_last_save_xbox(out) == [20190722, 2, f"hdfs://ns{out}/20190722/delta-2", key]
+    # per-pass full model + donefile.txt
+    assert u.save_model(out, 20190722, 2) == 120
+    assert u.write_model_donefile(out, 20190722, 2, key)
+    assert not u.write_model_donefile(out, 20190722, 2, key)
+    # end of day: base + batch model
+    assert u.save_xbox_base_model(out, 20190722) == 120 and os.path.isdir(f"{out}/20190722/base")
+    assert u.write_xbox_donefile(out, 20190722, -1, key, "/data")
+    base = json.loads(open(f"{out}/xbox_base_done.txt").read().strip())
+    assert base["id"] == str(key) and base["input"].endswith("/20190722/base/000")
+    assert u.get_last_save_xbox_base(out) == [20190722, f"{out}/20190722/base", key]
+    assert u.save_batch_model(out, 20190722) == 120 and os.path.isdir(f"{out}/20190722/0")
+    assert u.write_model_donefile(out, 20190722, -1, key)
+    rows = [r.split("\t") for r in open(f"{out}/donefile.txt").read().strip().split("\n")]
+    assert rows == [["20190722", str(key), f"{out}/20190722/2/", "2", "0"],
+                    ["20190722", str(key), f"{out}/20190722/0/", "-1", "0"]]
+    assert u.get_last_save_model(out) == [20190722, -1, f"{out}/20190722/0/", key]
+    # cache model: hot rows only, and its meta file
+    _touch(box, range(1, 11), clicks=40.0)
+    n_hot = u.save_cache_model(out, 20190722, 2, cache_threshold=30.0)
+    assert n_hot == 10
+    assert u.write_cache_donefile(out, 20190722, 2, n_hot) and not u.write_cache_donefile(out, 20190722, 2, n_hot)
+    assert open(f"{out}/20190722/delta-2/000_cache/sparse_cache.meta").read() == "file_prefix:part\npart_num:16\nkey_num:10\n"
+    # restart: a fresh wrapper resumes from what donefile.txt names
+    want = box.host_table.fetch_rows(np.arange(1, 121, dtype=np.uint64), create=False)
+    BoxWrapper.reset_instance()
+    b2 = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=0, world_size=1)
+    b2.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0})
+    u2 = FU.GPUPSUtil(box=b2)
+    day, pass_id, path, k = u2.get_last_save_model(out)
+    assert (day, pass_id, k) == (20190722, -1, key)
+    assert u2.load_model(out, day, pass_id) == 120
+    got = b2.host_table.fetch_rows(np.arange(1, 121, dtype=np.uint64), create=False)
+    # (the batch model was saved before the last 10 hot pushes)
+    assert np.allclose(got[10:], want[10:], rtol=1e-6)
+
+
+def test_global_metrics_come_from_the_metric_registry(box, capsys):
+    box.init_metric("AucCalculator", "join", "label", "pred", metric_phase=1, bucket_size=10000)
+    rng = np.random.default_rng(1)
+    p = torch.from_numpy(rng.random(5000).astype(np.float32))
+    y = (torch.from_numpy(rng.random(5000).astype(np.float32)) < p).float()
+    box.get_metric("join").add_data({"pred": p, "label": y})
+    u = FU.FleetUtil(box=box)
+    m = u.print_global_metrics("join", print_prefix="pass 1")
+    out = capsys.readouterr().out
+    assert "pass 1 global AUC=" in out and "Ins number=5000" in out
+    assert len(m) == 9 and 0.7 < m[0] < 0.9 and m[8] == 5000 and abs(m[4] - float(y.mean())) < 1e-6
+    assert u.get_global_metrics("nope") == [None] * 9
+    box.get_metric("join").add_data({"pred": p, "label": y})
+    u.set_zero("join")
+    assert u.get_global_metrics("join")[8] == 0
+
+
+def test_full_models_carry_the_dense_parameters_of_the_trainer(tmp_path, box):
+    from paddlebox_b200.models.ctr import CtrDnn
+    from paddlebox_b200.trainer import CTRTrainer, TrainerConfig
+    out = str(tmp_path / "o")
+    torch.manual_seed(0)
+    tr = CTRTrainer(CtrDnn(num_slots=3, embedx_dim=4, dense_dim=2, hidden=(8, 4)), box, TrainerConfig())
+    _touch(box, range(1, 20))
+    u = FU.FleetUtil(box=box, trainer=tr)
+    u.save_model(out, 20240101, 3)
+    assert os.path.isdir(f"{out}/20240101/3/dense")
+    assert set(u.pull_all_dense_params()) == {n for n, _ in tr.model.named_dense_params()}
+    plug = u.save_paddle_params(out, 20240101, 3)
+    assert plug.endswith("/20240101/3/dnn_plugin") and os.listdir(plug)
+    want = tr.store.flat.clone()
+    torch.manual_seed(1)
+    tr2 = CTRTrainer(CtrDnn(num_slots=3, embedx_dim=4, dense_dim=2, hidden=(8, 4)), box, TrainerConfig())
+    assert not torch.equal(tr2.store.flat, want)
+    FU.FleetUtil(box=box, trainer=tr2).load_model(out, 20240101, 3)
+    assert torch.allclose(tr2.store.flat, want)
