@@ -104,3 +104,122 @@ class _Util:
 
 
 util = _Util()
+
+
+# ---- the parameter-server calls of the reference's pslib fleet ------------------------------------------------
+# (python/paddle/fluid/incubate/fleet/parameter_server/pslib/__init__.py:214-800).  Job scripts written for the
+# CPU / GPU parameter server call these on ``fleet``; here they act on the process-wide wrapper (there is one
+# sparse table, so ``table_id`` arguments are accepted and not needed).
+def _box():
+    from .box_wrapper import BoxWrapper
+    return BoxWrapper.get_instance()
+
+
+def save_persistables(executor=None, dirname: str = "", main_program=None, mode: int = 0, **kwargs) -> int:
+    """``mode`` 0 = full state, 1 = delta (serving format, moves the delta baseline), 2 = serving base,
+    3 = batch model (pslib :348-370).  Returns the rows this worker wrote."""
+    box = _box()
+    box._sync_to_host()
+    n = box.host_table.save(dirname, mode=0 if mode == 3 else mode, shard_base=box.rank, clear_dirty=(mode == 1))
+    barrier_worker()
+    return n
+
+
+def save_model(model_dir: str | None = None, mode: int = 0, **kwargs) -> int:
+    return save_persistables(None, model_dir, mode=mode)
+
+
+def save_one_table(table_id, model_dir: str, mode: int = 0, **kwargs) -> int:
+    return save_persistables(None, model_dir, mode=mode)
+
+
+def save_multi_table_one_path(table_ids, model_dir: str, mode: int = 0, **kwargs) -> int:
+    return save_persistables(None, model_dir, mode=mode)
+
+
+def save_cache_model(executor=None, dirname: str = "", main_program=None, mode: int = 1, table_id: int = 0,
+                     cache_threshold: float = 1.0, **kwargs) -> int:
+    """Hot rows in serving format; returns the key count over all workers (pslib :429-469)."""
+    box = _box()
+    box._sync_to_host()
+    n = box.host_table.save(dirname, mode=2, shard_base=box.rank, base_threshold=cache_threshold, clear_dirty=False)
+    return int(util.all_reduce(int(n), "sum"))
+
+
+def load_model(model_dir: str | None = None, mode: int = 0, **kwargs) -> int:
+    n = _box().load_model(model_dir, serving=mode in (1, 2))
+    barrier_worker()
+    return n
+
+
+def load_one_table(table_id, model_path: str, mode: int = 0, **kwargs) -> int:
+    return load_model(model_path, mode=mode)
+
+
+def shrink_sparse_table(decay: float = 0.98, delete_threshold: float = 0.0, delete_after_unseen_days: float = 30.0) -> int:
+    """Day-end decay of show / click and removal of stale rows (pslib :471-486); returns the rows removed here."""
+    box = _box()
+    box._sync_to_host()
+    before = box.host_table.size()
+    kept = box.shrink_table(decay, delete_threshold, delete_after_unseen_days)
+    barrier_worker()
+    return before - kept
+
+
+def shrink_dense_table(decay: float, emb_dim: int = 11, scope=None, table_id=None, trainer=None) -> None:
+    """Decay the data-norm summaries of the dense part (pslib :488-521 multiplies the ``batch_size`` /
+    ``batch_sum`` / ``batch_square_sum`` parameters by ``decay``).  ``trainer``: the ``CTRTrainer`` whose model
+    holds them."""
+    if trainer is None:
+        return
+    import torch
+    with torch.no_grad():
+        for m in trainer.model.modules():
+            for name in ("batch_size", "batch_sum", "batch_square_sum"):
+                t = getattr(m, name, None)
+                if isinstance(t, torch.Tensor):
+                    t.mul_(decay)
+    barrier_worker()
+
+
+def clear_one_table(table_id=None) -> None:
+    clear_model()
+
+
+def clear_model() -> None:
+    """Drop every sparse row (host tier and HBM shard) — a job that restarts training from scratch (pslib :537)."""
+    box = _box()
+    box.host_table.clear()
+    if getattr(box, "table", None) is not None:
+        box.table.clear()
+    barrier_worker()
+
+
+def print_table_stat(table_id=None) -> dict:
+    """Rows in memory / on the SSD tier of this worker's shard (pslib :318-331 prints the server's counters)."""
+    box = _box()
+    stat = {"rank": worker_index(), "mem_rows": box.host_table.mem_rows() if hasattr(box.host_table, "mem_rows")
+            else box.host_table.size(), "ssd_rows": box.host_table.ssd_rows() if box._ssd else 0,
+            "rows": box.host_table.size()}
+    print(f"[table stat] {stat}")
+    return stat
+
+
+def set_date(table_id, date) -> None:
+    _box().set_date(str(date))
+
+
+def set_file_num_one_shard(table_id, file_num: int) -> None:
+    """Accepted: a shard is always written as one ``part-<rank>-<shard>`` file here."""
+
+
+def end_pass(scope=None) -> None:
+    _box().end_pass()
+
+
+def distributed_optimizer(optimizer, strategy=None):
+    """The reference wraps the optimizer into a ``DownpourOptimizer`` that rewrites the program for the PS
+    (pslib :281-294).  Here the wrapper's ``minimize`` only records the choice: the sparse part is optimized
+    inside the table, the dense part by ``CTRTrainer``'s flat optimizer configured from ``optimizer``."""
+    from .optimizer import BoxPSOptimizer
+    return optimizer if isinstance(optimizer, BoxPSOptimizer) else BoxPSOptimizer(optimizer)

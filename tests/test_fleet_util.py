@@ -158,3 +158,31 @@ def test_full_models_carry_the_dense_parameters_of_the_trainer(tmp_path, box):
     assert not torch.equal(tr2.store.flat, want)
     FU.FleetUtil(box=box, trainer=tr2).load_model(out, 20240101, 3)
     assert torch.allclose(tr2.store.flat, want)
+
+
+def test_pslib_style_fleet_calls_act_on_the_wrapper(tmp_path, box):
+    from paddlebox_b200 import fleet
+    from paddlebox_b200.ops.functional import DataNorm
+    _touch(box, range(1, 51))
+    d0 = str(tmp_path / "full")
+    assert fleet.save_persistables(None, d0, mode=0) == 50
+    assert fleet.save_persistables(None, str(tmp_path / "delta"), mode=1) == 50
+    assert fleet.save_persistables(None, str(tmp_path / "delta2"), mode=1) == 0      # the baseline moved
+    _touch(box, range(1, 6), clicks=50.0)
+    assert fleet.save_cache_model(None, str(tmp_path / "cache"), cache_threshold=30.0) == 5
+    st = fleet.print_table_stat(0)
+    assert st["rows"] == 50 and st["rank"] == 0
+    fleet.clear_model()
+    assert box.host_table.size() == 0
+    assert fleet.load_model(d0) == 50 and box.host_table.size() == 50
+    removed = fleet.shrink_sparse_table(decay=0.5, delete_threshold=1e9)              # nothing survives this bar
+    assert removed == 50 and box.host_table.size() == 0
+    fleet.set_date(0, 20240105)
+
+    class T:                                                                          # a trainer-shaped holder
+        model = torch.nn.Sequential(DataNorm(4))
+    before = T.model[0].batch_size.clone()
+    fleet.shrink_dense_table(0.9, trainer=T)
+    assert torch.allclose(T.model[0].batch_size, before * 0.9)
+    from paddlebox_b200.optimizer import BoxPSOptimizer
+    assert isinstance(fleet.distributed_optimizer(object()), BoxPSOptimizer)
