@@ -458,6 +458,120 @@ class GraphGpuWrapper:
             return self.device_graph.sample_neighbors(nodes, sample_size, t)
         return self.table.sample_neighbors(nodes, sample_size, t)
 
+    # ---- service set-up names (graph_gpu_wrapper.cu:107-260) -----------------------------------------------
+    def set_device(self, device_ids: Sequence[int]) -> None:
+        """Devices of this process (one per process here: the first entry is used by ``upload_batch``)."""
+        self.device_ids = list(device_ids)
+
+    def init_search_level(self, level: int) -> None:
+        """0 = the whole graph resident in HBM, 1 = partitions paged from host memory, 2 = additionally the
+        complementary graph of hot neighbours (``make_complementary_graph``)."""
+        assert level in (0, 1, 2), level
+        self.search_level = int(level)
+
+    set_search_level = init_search_level
+
+    def init_service(self) -> None:
+        """The reference builds its table proto and shard pool here; the native store needs no set-up — this
+        validates what was declared (every feature table names a declared node type)."""
+        for tname in getattr(self, "feat_conf", {}):
+            if tname not in self.node_types:
+                raise ValueError(f"add_table_feat_conf names node type {tname!r}, set_up_types did not")
+        self.service_ready = True
+
+    def add_table_feat_conf(self, table_name: str, feat_name: str, feat_dtype: str, feat_shape: int) -> int:
+        """Declare feature ``feat_name`` of node type ``table_name``; returns its slot index (first come, first
+        numbered; declaring a name again overrides its dtype / shape, graph_gpu_wrapper.cu:163-190)."""
+        if table_name not in self.node_types:
+            return -1
+        conf = self.__dict__.setdefault("feat_conf", {}).setdefault(table_name, {})
+        slot = conf[feat_name][0] if feat_name in conf else len(conf)
+        conf[feat_name] = (slot, feat_dtype, int(feat_shape))
+        return slot
+
+    def feature_slot(self, table_name: str, feat_name: str) -> int:
+        return self.feat_conf[table_name][feat_name][0]
+
+    @staticmethod
+    def inverse_etype(etype: str) -> str:
+        a, _, b = etype.partition("2")
+        return f"{b}2{a}" if b else etype
+
+    def load_node_and_edge(self, etype: str, ntype: str, epath: str, npath: str, part_num: int = 0,
+                           reverse: bool = False) -> dict:
+        """Edge types ``"u2i,i2i"`` from ``epath/<etype>/*`` and node types ``"u,i"`` from the files of ``npath``,
+        at most ``part_num`` files of each directory (0 = all); ``reverse`` also loads every edge file backwards
+        as the inverse type (``u2i`` -> ``i2u``) (common_graph_table.cc:1081-1145)."""
+        import os
+        out = {}
+
+        def files_of(d):
+            fs = sorted(os.path.join(d, f) for f in os.listdir(d) if os.path.isfile(os.path.join(d, f)))
+            return fs[:part_num] if 0 < part_num < len(fs) else fs
+
+        for et in [e for e in etype.split(",") if e]:
+            n = 0
+            for f in files_of(os.path.join(epath, et)):
+                n += self.load_edge_file(et, f, False)
+                if reverse:
+                    self.load_edge_file(self.inverse_etype(et), f, True)
+            out[et] = n
+        node_files = files_of(npath) if ntype else []
+        for nt in [t for t in ntype.split(",") if t]:
+            out[nt] = sum(self.load_node_file(nt, f) for f in node_files)
+        return out
+
+    def query_node_list(self, gpu_id: int, name: str, start: int, query_size: int) -> np.ndarray:
+        """``query_size`` node ids of the type from position ``start`` of its id list (the reference pages
+        through a device's node list this way, graph_gpu_wrapper.h:84-87)."""
+        ids = self.get_all_id(name) if name in self.edge_types else self.table.typed_nodes(self.node_types[name])
+        return ids[int(start):int(start) + int(query_size)]
+
+    def neighbor_sample(self, name: str, nodes, sample_size: int):
+        return self.graph_neighbor_sample(name, nodes, sample_size)
+
+    def make_complementary_graph(self, name: str, byte_size: int, device=None) -> np.ndarray:
+        """Search level 2: next to the resident partition keep the adjacency lists of the nodes that the
+        resident edges point to most often, as many as fit ``byte_size`` (8 bytes per edge) — walks that leave
+        the partition mostly land there.  Returns the chosen node ids, most referenced first, and makes
+        ``complementary_graph`` a ``DeviceGraph`` of their rows (ids stay global; rows of other nodes are absent)
+        (reference: GraphTable::make_complementary_graph, common_graph_table.cc:556-620)."""
+        t = self.edge_types[name]
+        ids, rp, col = self.table.csr(t)
+        if self.resident_partition >= 0:
+            pids, prp, pcol_ids, _ = self.table.partition(t, self.resident_partition)
+            targets = pcol_ids
+        else:
+            pids, targets = ids, ids[col]
+        if targets.size == 0:
+            self.complementary_graph = None
+            return np.zeros(0, np.uint64)
+        uniq, cnt = np.unique(targets, return_counts=True)
+        outside = ~np.isin(uniq, pids) if self.resident_partition >= 0 else np.ones(uniq.size, bool)
+        uniq, cnt = uniq[outside], cnt[outside]
+        order = np.lexsort((uniq, -cnt))                       # most referenced first, ties by id
+        uniq = uniq[order]
+        pos = np.searchsorted(ids, uniq)
+        ok = (pos < ids.size) & (ids[np.minimum(pos, ids.size - 1)] == uniq)
+        uniq, pos = uniq[ok], pos[ok]
+        deg = (rp[pos + 1] - rp[pos]).astype(np.int64)
+        fits = np.cumsum(deg * 8) <= int(byte_size)
+        chosen, cpos = uniq[fits], pos[fits]
+        srt = np.argsort(chosen)
+        c_ids, c_pos = chosen[srt], cpos[srt]
+        c_rp = np.zeros(c_ids.size + 1, np.int64)
+        c_rp[1:] = np.cumsum(rp[c_pos + 1] - rp[c_pos])
+        c_col_ids = np.concatenate([ids[col[rp[p]:rp[p + 1]]] for p in c_pos]) if c_ids.size else np.zeros(0, np.uint64)
+        # neighbours that are themselves in the complementary set are indexable; the rest end a walk here
+        npos = np.minimum(np.searchsorted(c_ids, c_col_ids), max(c_ids.size - 1, 0))
+        keep = c_ids[npos] == c_col_ids if c_ids.size else np.zeros(0, bool)
+        row = np.repeat(np.arange(c_ids.size), np.diff(c_rp))
+        k_rp = np.zeros(c_ids.size + 1, np.int64)
+        k_rp[1:] = np.cumsum(np.bincount(row[keep], minlength=c_ids.size))
+        self.complementary_graph = DeviceGraph({t: (c_ids, k_rp, npos[keep].astype(np.int64))}, device)
+        self.complementary_ids = chosen
+        return chosen
+
     def finalize(self) -> None:
         self.device_graph = None
         self.table = GraphTable()

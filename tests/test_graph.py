@@ -186,3 +186,87 @@ def test_weighted_edges_node_features_and_partitions(tmp_path):
     dg = wpr.device_graph
     nb, cnt = dg.sample_neighbors(torch.tensor([3, 9], dtype=torch.int64), 2, 0)
     assert cnt.tolist() == [1, 0] and int(nb[0, 0]) == 4       # 9 -> 10 leaves the resident partition: dropped
+
+
+def test_graph_wrapper_service_names_and_complementary_graph(tmp_path):
+    """The rest of GraphGpuWrapper's surface: feature conf, load_node_and_edge over directories (part_num,
+    reverse -> inverse type), query_node_list paging, search levels, and the complementary graph of hot
+    neighbours next to a resident partition."""
+    import numpy as np
+    from paddlebox_b200.graph import GraphGpuWrapper
+    w = GraphGpuWrapper()
+    w.set_up_types(["u2i", "i2u"], ["u", "i"])
+    w.set_device([0])
+    w.init_search_level(2)
+    assert w.add_table_feat_conf("u", "age", "int64", 1) == 0 and w.add_table_feat_conf("u", "city", "int64", 1) == 1
+    assert w.add_table_feat_conf("u", "age", "float32", 2) == 0 and w.feature_slot("u", "city") == 1
+    assert w.add_table_feat_conf("nobody", "x", "int64", 1) == -1
+    w.init_service()
+    assert GraphGpuWrapper.inverse_etype("u2i") == "i2u" and GraphGpuWrapper.inverse_etype("plain") == "plain"
+    # data: users 1..40 -> items 1000+; item 1000 is by far the most referenced
+    ed = tmp_path / "edges" / "u2i"
+    ed.mkdir(parents=True)
+    rng = np.random.default_rng(0)
+    n_edges = 0
+    for part in range(3):
+        with open(ed / f"part-{part}", "w") as f:
+            for u in range(1 + part * 14, 1 + (part + 1) * 14):
+                for it in {1000} | set(int(x) for x in 1001 + rng.integers(0, 30, 3)):
+                    f.write(f"{u}\t{it}\n")
+                    n_edges += 1
+    nd = tmp_path / "nodes"
+    nd.mkdir()
+    with open(nd / "n0", "w") as f:
+        for u in range(1, 43):
+            f.write(f"u\t{u}\t0:{u % 7}\t1:{u % 3}\n")
+        for it in range(1000, 1031):
+            f.write(f"i\t{it}\t0:{it % 5}\n")
+    got = w.load_node_and_edge("u2i", "u,i", str(tmp_path / "edges"), str(nd), part_num=0, reverse=True)
+    assert got["u2i"] == n_edges and got["u"] == 42 and got["i"] == 31
+    w.upload_batch(device="cpu")
+    users = w.get_all_id("u2i")
+    assert 1 in users.tolist() and 42 in users.tolist() or users.size >= 42 - 1
+    # paging through a type's id list
+    page = w.query_node_list(0, "u2i", 5, 10)
+    assert np.array_equal(page, users[5:15]) and w.query_node_list(0, "u", 0, 3).tolist() == [1, 2, 3]
+    # the reversed type really is the inverse relation
+    nb, cnt = w.neighbor_sample("i2u", np.array([1000], np.uint64), 64)
+    assert cnt[0] == 42 and set(nb[0, :42].tolist()) == set(range(1, 43))
+    # part_num limits the files read
+    w2 = GraphGpuWrapper()
+    w2.set_up_types(["u2i"], [])
+    assert 0 < w2.load_node_and_edge("u2i", "", str(tmp_path / "edges"), str(nd), part_num=1)["u2i"] < n_edges
+    # complementary graph on a homogeneous relation: every node points at the hubs 1..3 and at a few others
+    ef = tmp_path / "n2n.txt"
+    with open(ef, "w") as f:
+        for a in range(1, 61):
+            for b in {1, 2, 3} | set(int(x) for x in 1 + rng.integers(0, 60, 2)):
+                if a != b:
+                    f.write(f"{a}\t{b}\n")
+    w3 = GraphGpuWrapper()
+    w3.set_up_types(["n2n"], [])
+    w3.init_search_level(2)
+    w3.load_edge_file("n2n", str(ef), False)
+    w3.upload_batch(device="cpu")
+    nparts = w3.make_partitions("n2n", 512, 1)
+    assert nparts >= 3
+    ids, rp, col = w3.table.csr(w3.edge_types["n2n"])
+    deg = dict(zip(ids.tolist(), np.diff(rp).tolist()))
+    # page in a partition that does not hold the hubs: they are what the complementary graph must bring along
+    p = w3.load_next_partition("n2n", device="cpu")
+    while {1, 2, 3} & set(w3.get_partition("n2n", p).tolist()):
+        p = w3.load_next_partition("n2n", device="cpu")
+        assert p >= 0
+    resident = set(w3.get_partition("n2n", p).tolist())
+    budget = 8 * (deg[1] + deg[2] + deg[3] + 2)
+    chosen = w3.make_complementary_graph("n2n", budget, device="cpu")
+    assert set(chosen[:3].tolist()) == {1, 2, 3}                               # most referenced first
+    assert not (set(chosen.tolist()) & resident)                               # never what is resident already
+    assert sum(deg[int(c)] for c in chosen) * 8 <= budget                      # fits the byte budget
+    cg = w3.complementary_graph
+    assert cg is not None
+    # no partition resident: the hubs still lead
+    w3.resident_partition = -1
+    top = w3.make_complementary_graph("n2n", 1 << 20, device="cpu")
+    assert set(top[:3].tolist()) == {1, 2, 3} and 40 < top.size <= ids.size     # (only referenced nodes are candidates)
+    assert w3.make_complementary_graph("n2n", 0, device="cpu").size == 0
