@@ -14,6 +14,8 @@ from .ops.ctr_ops import (BatchFC, CrossNormHadamard, batch_fc, build_rank_offse
                           rank_attention, rank_attention2, scaled_fc, scaled_int8fc, shuffle_batch)
 from .ops.functional import (DataNorm, continuous_value_model, ctr_head, data_norm, fm_interaction,  # noqa: F401
                              masked_data_norm, sigmoid_log_loss, store_q_value, stored_q_values)
+from .ops.misc_layers import (fused_elemwise_activation, fused_embedding_seq_pool,  # noqa: F401
+                              pow2_decay_with_linear_warmup, sparse_embedding)
 from .ops.pull_box_sparse import (SlotBatch, pull_box_extended_sparse, pull_box_sparse, sparse_embedding_pool,  # noqa: F401
                                   split_by_slot)
 from .ops.seqpool import (SeqpoolAttrs, fused_seqpool_cvm, fused_seqpool_cvm_tradew, fused_seqpool_cvm_with_conv,  # noqa: F401

@@ -676,3 +676,46 @@ def test_debug_flags_are_wired(tmp_path, box, capsys):
         FLAGS.enable_debug_print_metrics_info = False
         FLAGS.padbox_dump_debug_lineid = ""
         FLAGS.gpu_replica_cache_dim = 8
+
+
+def test_remaining_contrib_layer_names():
+    import torch
+    from paddlebox_b200 import layers as L
+    torch.manual_seed(0)
+    w = torch.randn(10, 4, requires_grad=True)
+    ids = torch.tensor([1, 2, 9, 3, 9, 0])
+    lod = torch.tensor([0, 2, 2, 6])
+    out = L.fused_embedding_seq_pool(ids, lod, w, padding_idx=-1)          # -1 = id 9 is padding
+    want = torch.stack([w[1] + w[2], torch.zeros(4), w[3] + w[0]])
+    assert torch.allclose(out, want)
+    out.sum().backward()
+    assert torch.allclose(w.grad[9], torch.zeros(4)) and torch.allclose(w.grad[1], torch.ones(4))
+    x, y = torch.randn(3, 4), torch.randn(3, 4)
+    o, mid = L.fused_elemwise_activation(x, y, ["elementwise_add", "relu"])
+    assert torch.allclose(o, x + torch.relu(y)) and torch.allclose(mid, torch.relu(y))
+    o = L.fused_elemwise_activation(x, y, "scale,elementwise_mul", scale=0.5, save_intermediate_out=False)
+    assert torch.allclose(o, 0.5 * x * y)
+    yb = torch.randn(3)
+    o = L.fused_elemwise_activation(x, yb, ["tanh", "elementwise_add"], axis=0, save_intermediate_out=False)
+    assert torch.allclose(o, torch.tanh(x + yb[:, None]))
+    lr = L.pow2_decay_with_linear_warmup(10, 110, 0.1, 0.01)
+    assert abs(lr(5) - 0.05) < 1e-12 and abs(lr(10) - 0.1) < 1e-12 and abs(lr(60) - (0.09 * 0.25 + 0.01)) < 1e-12
+    assert lr(110) == 0.01 and lr(500) == 0.01 and L.pow2_decay_with_linear_warmup(10, 110, 0.1, 0.01, step=10) == lr(10)
+    # sparse_embedding: per-id embedx rows of the wrapper
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    from paddlebox_b200.ops.pull_box_sparse import SlotBatch
+    BoxWrapper.reset_instance()
+    try:
+        box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=0, world_size=1)
+        box.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0, "mf_initial_range": 0.1})
+        keys = torch.tensor([11, 12, 0, 11], dtype=torch.int64)
+        batch = SlotBatch(keys, torch.tensor([0, 2, 4], dtype=torch.int32), 2, 1, torch.zeros(2, 1))
+        box.begin_feed_pass("20240101"); box.feed_pass(keys); box.end_feed_pass(); box.begin_pass()
+        e = L.sparse_embedding(batch, [1 << 40, 4], padding_idx=12)
+        assert e.shape == (4, 4) and torch.equal(e[0], e[3]) and torch.equal(e[1], torch.zeros(4))
+        import pytest
+        with pytest.raises(ValueError):
+            L.sparse_embedding(batch, 8)
+        box.end_pass()
+    finally:
+        BoxWrapper.reset_instance()
