@@ -621,6 +621,25 @@ class QueueDataset(InMemoryDataset):
         self.stream_stats["max_resident_records"] = max(self.stream_stats["max_resident_records"], n_cur)
 
 
+class FileInstantDataset(QueueDataset):
+    """``FileInstantDataset`` (python/paddle/fluid/dataset.py:1193-1229, ``MultiSlotFileInstantDataFeed``): files
+    are only ever processed as a stream — the streaming path of :class:`QueueDataset` with the in-memory
+    fallback removed."""
+
+    def load_into_memory(self):
+        raise NotImplementedError("FileInstantDataset processes files as a stream; use InMemoryDataset to load a pass")
+
+    preload_into_memory = load_into_memory
+
+    def local_shuffle(self):
+        raise NotImplementedError("FileInstantDataset does not support local shuffle, please use InMemoryDataset "
+                                  "for local_shuffle")
+
+    def global_shuffle(self, fleet=None, thread_num=12):
+        raise NotImplementedError("FileInstantDataset does not support global shuffle, please use InMemoryDataset "
+                                  "for global_shuffle")
+
+
 class BoxPSDataset(InMemoryDataset):
     """Dataset bound to the BoxWrapper pass lifecycle (``BoxHelper``, box_wrapper.h:1043-1295):
     ``load_into_memory`` = BeginFeedPass -> read + collect keys -> EndFeedPass."""
@@ -731,6 +750,7 @@ class InputTableDataset(PadBoxSlotDataset):
 class DatasetFactory:
     """``DatasetFactory().create_dataset("PadBoxSlotDataset")`` (dataset.py:30-63)."""
     _KINDS = {"InMemoryDataset": InMemoryDataset, "QueueDataset": QueueDataset, "BoxPSDataset": BoxPSDataset,
+              "FileInstantDataset": FileInstantDataset,
               "PadBoxSlotDataset": PadBoxSlotDataset, "InputTableDataset": InputTableDataset,
               "SlotRecordDataset": InMemoryDataset, "MultiSlotDataset": InMemoryDataset}
 

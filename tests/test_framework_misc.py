@@ -613,6 +613,11 @@ def test_queue_dataset_streams_without_loading_the_pass(tmp_path):
     assert ds.stream_stats["records"] == 5 * 37 and ds.stream_stats["groups"] == 5
     assert ds.stream_stats["max_resident_records"] <= 2 * 37          # two groups at most, never the pass
     assert ds.get_memory_data_size() == 0                             # the dataset itself holds nothing
+    fi = DatasetFactory().create_dataset("FileInstantDataset")
+    fi.set_use_var(slot_vars(3, 2)); fi.set_batch_size(8); fi.set_thread(1); fi.set_filelist(files[:2])
+    with pytest.raises(NotImplementedError):
+        fi.load_into_memory()
+    assert sum(b.batch_size for b in fi.batches(device=torch.device("cpu"))) == 2 * 37
     # several files per group with several readers: nothing lost, nothing doubled
     ds.set_thread(2)
     assert [len(g) for g in ds.file_groups()] == [2, 2, 1]
