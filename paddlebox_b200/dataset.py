@@ -129,6 +129,70 @@ class DatasetBase:
         else:
             self._native.set("pipe_command", pipe_command)
 
+    # ---- the rest of the reference's DatasetBase surface (python/paddle/fluid/dataset.py:66-395) -------------------
+    def set_uid_slot(self, uid_slot: str):
+        """Name of the slot whose first feasign is the user id of the instance (``MultiSlotDesc.uid_slot``,
+        data_feed.cc:1101, :1222): the per-user metrics read it (``uid_of_batch``) and ``set_shuffle_by_uid``
+        partitions by it."""
+        self.uid_slot = uid_slot
+
+    def uid_of_batch(self, batch) -> "torch.Tensor":
+        """[B] user ids of a ``SlotBatch``: the first key of the uid slot of every instance (0 for an empty bag)."""
+        names = [s.name for s in self.all_slots if s.is_used and s.lod_level > 0]
+        si = names.index(self.uid_slot)
+        B = batch.batch_size
+        lod = batch.lod[si * B:(si + 1) * B + 1].long()
+        first = batch.keys[lod[:-1].clamp(max=max(batch.keys.numel() - 1, 0))]
+        return torch.where(lod[1:] > lod[:-1], first, torch.zeros_like(first))
+
+    def set_input_type(self, input_type: int):
+        """0 = one sample per generated record, 1 = one batch (``DataFeedDesc.input_type``)."""
+        self.input_type = int(input_type)
+
+    def set_so_parser_name(self, so_parser_name: str):
+        """Parser plugin library (``DataFeedDesc.so_parser_name``): same as giving the ``.so`` as pipe command."""
+        self.so_parser_name = so_parser_name
+        if so_parser_name:
+            self.set_pipe_command(so_parser_name)
+
+    def set_feed_type(self, data_feed_type: str):
+        """Name of the native feed class.  The SlotRecord feed is the one implementation here; the Record-based
+        ``MultiSlot*`` feeds are ``paddlebox_b200.legacy_feed``."""
+        self.data_feed_type = data_feed_type
+
+    def _set_use_ps_gpu(self, psgpu):
+        """Bind the dataset to a ``PSGPUWrapper`` (``set_date`` then reaches it; dataset.py:347-359)."""
+        self.use_ps_gpu, self.psgpu = psgpu is not None, psgpu
+
+    def _set_heter_ps(self, enable_heter_ps: bool = False):
+        self.enable_heter_ps = bool(enable_heter_ps)
+
+    def _set_trainer_num(self, trainer_num: int):
+        self.trainer_num = int(trainer_num)
+
+    def set_graph_config(self, config: dict):
+        """Graph-walk feed configuration (walk_degree, walk_len, window, batch_size, meta_path ...): kept for
+        ``paddlebox_b200.graph.GraphDataGenerator(**config)``."""
+        self.graph_config = dict(config)
+
+    def _prepare_to_run(self):
+        """Before a pass: no more reader threads than files, at least one (dataset.py:336-345, :426-447)."""
+        n = max(1, min(int(self.thread_num), max(len(self.filelist), 1)))
+        if n != self.thread_num:
+            self.set_thread(n)
+
+    def _finish_to_run(self):
+        """After a pass the reference destroys its readers; reader threads here end with ``load_into_memory``."""
+
+    def _dynamic_adjust_before_train(self, thread_num: int):
+        """The trainer runs with ``thread_num`` workers: deal the loaded pass to that many (dataset.py:450-460)."""
+        self._adjusted_from = getattr(self, "_prepared_workers", 0)
+        if getattr(self, "_prepared_workers", 0) not in (0, int(thread_num)) and self._native.num_records() > 0:
+            self.prepare_train(int(thread_num))
+
+    def _dynamic_adjust_after_train(self):
+        self._adjusted_from = 0
+
     def set_hdfs_config(self, fs_name: str, fs_ugi: str):
         self.fs_name, self.fs_ugi = fs_name, fs_ugi
 
@@ -189,6 +253,15 @@ class DatasetBase:
         return self._native.dense_dim()
 
 
+def _alias_private_setters(cls):
+    """The fleet flavour of the dataset API (python/paddle/distributed/fleet/dataset/dataset.py) spells its setters
+    ``_set_x`` and has users go through ``init(**kwargs)`` / ``update_settings(**kwargs)``: both spellings work."""
+    for name in list(vars(cls)):
+        if name.startswith("set_") and not hasattr(cls, "_" + name):
+            setattr(cls, "_" + name, getattr(cls, name))
+    return cls
+
+
 class InMemoryDataset(DatasetBase):
     """Loads a pass into host memory, shuffles, deals equal batch counts to the workers."""
 
@@ -204,6 +277,17 @@ class InMemoryDataset(DatasetBase):
         self._worker = 0
 
     # setters (dataset.py:372-1105) -----------------------------------------------------------
+    def set_date(self, date: str):
+        """Training date (``YYYYMMDD``) for pulls, saves and loads — reaches the bound wrapper
+        (``_set_use_ps_gpu``) or the process-wide ``BoxWrapper`` (dataset.py:740-761)."""
+        self._date = str(date)
+        ps = getattr(self, "psgpu", None)
+        if ps is None:
+            from .box_wrapper import BoxWrapper
+            ps = BoxWrapper._instance if hasattr(BoxWrapper, "_instance") else None
+        if ps is not None:
+            ps.set_date(self._date)
+
     def set_parse_ins_id(self, v: bool):
         self.parse_ins_id = bool(v)
         self._native.set("parse_ins_id", int(v))
@@ -718,6 +802,11 @@ class InputTableDataset(PadBoxSlotDataset):
     def set_input_table_dim(self, dim: int):
         self.input_table_dim = int(dim)
 
+    def set_index_parser(self, index_parser: str):
+        """Parser plugin for the INDEX files (``DataFeedDesc.index_parser``; the data files keep the dataset's own
+        parser).  A library given here must export the line-parser ABI of ``csrc/host/dataset.cc``."""
+        self.index_parser = index_parser
+
     @property
     def input_table(self):
         """The ``InputTable`` of the current BoxWrapper (created on first use)."""
@@ -745,6 +834,41 @@ class InputTableDataset(PadBoxSlotDataset):
         # a parser plugin that exports pbx_set_offset_func resolves string keys at parse time
         self._native.set_input_index(self.input_table.handle)
         super().load_into_memory()
+
+
+def _update_settings(self, **kwargs):
+    """``update_settings(**kwargs)`` / ``_init_distributed_settings(**kwargs)`` of the fleet flavour: every key
+    is a setter without its ``set_`` prefix (``batch_size``, ``thread_num``, ``use_var``, ``pipe_command``,
+    ``input_type``, ``fs_name`` + ``fs_ugi``, ``download_cmd``, ``data_feed_type``, ``queue_num``, ``merge_size``,
+    ``parse_ins_id``, ``parse_content``, ``fleet_send_batch_size``, ``fleet_send_sleep_seconds``, ``fea_eval`` +
+    ``candidate_size``, ...)."""
+    kw = dict(kwargs)
+    if "fs_name" in kw or "fs_ugi" in kw:
+        self.set_hdfs_config(kw.pop("fs_name", getattr(self, "fs_name", "")), kw.pop("fs_ugi", getattr(self, "fs_ugi", "")))
+    if "thread_num" in kw:
+        self.set_thread(kw.pop("thread_num"))
+    if "merge_size" in kw:
+        m = kw.pop("merge_size")
+        if m and m > 0:
+            self.set_merge_by_lineid(m)
+    if "data_feed_type" in kw:
+        self.set_feed_type(kw.pop("data_feed_type"))
+    if kw.pop("fea_eval", False):
+        self.set_fea_eval(kw.pop("candidate_size", 10000), True)
+    kw.pop("candidate_size", None)
+    for k, v in kw.items():
+        setter = getattr(self, "set_" + k, None)
+        if setter is None:
+            raise TypeError(f"unknown dataset setting {k!r}")
+        if v is not None:
+            setter(v)
+
+
+for _cls in (DatasetBase, InMemoryDataset, QueueDataset, FileInstantDataset, BoxPSDataset, PadBoxSlotDataset,
+             InputTableDataset):
+    _alias_private_setters(_cls)
+DatasetBase.update_settings = _update_settings
+DatasetBase._init_distributed_settings = _update_settings
 
 
 class DatasetFactory:

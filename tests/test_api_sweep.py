@@ -719,3 +719,81 @@ def test_remaining_contrib_layer_names():
         box.end_pass()
     finally:
         BoxWrapper.reset_instance()
+
+
+def test_dataset_surface_matches_both_reference_flavours():
+    """Every public (and fleet-flavour ``_set_*``) method name of the reference's dataset classes exists here,
+    and the added ones do what they say."""
+    import re
+    import paddlebox_b200.dataset as D
+    from tests.util_data import slot_vars
+    refs = ["/root/reference/python/paddle/fluid/dataset.py",
+            "/root/reference/python/paddle/distributed/fleet/dataset/dataset.py"]
+    import os
+    if all(os.path.exists(r) for r in refs):
+        skip = {"_check_use_var_with_data_generator", "_desc", "_generate_local_tables_unlock"}   # proto / pslib internals
+        for path in refs:
+            cur = None
+            for ln in open(path):
+                m = re.match(r"class (\w+)", ln)
+                if m:
+                    cur = m.group(1)
+                m = re.match(r"    def (\w+)", ln)
+                if m and cur and not m.group(1).startswith("__") and m.group(1) not in skip:
+                    # (every concrete dataset here derives from InMemoryDataset, which carries the setters the
+                    # reference keeps on DatasetBase)
+                    cls = D.InMemoryDataset if cur == "DatasetBase" else getattr(D, cur)
+                    assert hasattr(cls, m.group(1)), f"{cur}.{m.group(1)} ({path})"
+    ds = D.DatasetFactory().create_dataset("InMemoryDataset")
+    ds.init(batch_size=4, thread_num=3, use_var=slot_vars(2, 1), pipe_command="cat", input_type=1)
+    ds.update_settings(batch_size=8, thread_num=2, merge_size=2, parse_ins_id=True, fs_name="hdfs://x", fs_ugi="u,p",
+                       data_feed_type="SlotRecordInMemoryDataFeed", queue_num=4, fea_eval=True, candidate_size=77)
+    assert (ds.batch_size, ds.thread_num, ds.fs_name, ds.data_feed_type, ds.parse_ins_id) == \
+        (8, 2, "hdfs://x", "SlotRecordInMemoryDataFeed", True)
+    ds._set_batch_size(16)
+    assert ds.batch_size == 16
+    import pytest
+    with pytest.raises(TypeError):
+        ds.update_settings(no_such_setting=1)
+    ds.set_filelist(["a"])
+    ds.set_thread(8)
+    ds._prepare_to_run()
+    assert ds.thread_num == 1                                      # no more readers than files
+    ds._finish_to_run(); ds._dynamic_adjust_before_train(2); ds._dynamic_adjust_after_train()
+    ds._set_trainer_num(4); ds._set_heter_ps(True); ds.set_graph_config({"walk_len": 8})
+    assert ds.trainer_num == 4 and ds.graph_config["walk_len"] == 8
+
+    class PS:
+        date = None
+
+        def set_date(self, d):
+            self.date = d
+    ps = PS()
+    ds._set_use_ps_gpu(ps)
+    ds.set_date("20240107")
+    assert ps.date == "20240107"
+    it = D.DatasetFactory().create_dataset("InputTableDataset")
+    it.set_index_parser("libidx.so"); it.set_feed_type("InputTableDataFeed")
+    assert it.index_parser == "libidx.so"
+
+
+def test_uid_slot_gives_the_user_id_of_every_instance(tmp_path):
+    import torch
+    import paddlebox_b200.dataset as D
+    from tests.util_data import slot_vars, write_files
+    files = write_files(str(tmp_path), n_files=1, lines_per_file=12, n_sparse=3, n_dense=1, key_space=100)
+    ds = D.DatasetFactory().create_dataset("InMemoryDataset")
+    ds.set_use_var(slot_vars(3, 1)); ds.set_batch_size(4); ds.set_thread(1); ds.set_merge_thread_num(1)
+    ds.set_filelist(files)
+    ds._set_uid_slot("slot1")
+    ds.load_into_memory()
+    ds.prepare_train(1, shuffle=False)
+    uids = torch.cat([ds.uid_of_batch(b) for b in ds.batches(device=torch.device("cpu"))])
+    # label(1) + dense(1) = tokens 0..3; then slot0: n v..; slot1: n v...
+    want = []
+    for line in open(files[0]):
+        t = line.split()
+        p = 4
+        n0 = int(t[p]); p += 1 + n0
+        want.append(int(t[p + 1]))
+    assert uids.tolist() == want
