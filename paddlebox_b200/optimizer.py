@@ -105,6 +105,10 @@ class LocalSGD(GradAllReduce):
         self.mode = "kstep"
         self.k_steps = k_steps
 
+    @staticmethod
+    def snapshot_name(param_name: str) -> str:
+        return param_name + "@SNAPSHOT"
+
     def transpile(self, startup_program=None, main_program=None, **kw):
         mode = super().transpile(startup_program, main_program, **kw)
         if main_program is not None and getattr(main_program, "_pipeline_opt", None):
@@ -116,6 +120,23 @@ class SingleProcessMultiThread(GradAllReduce):
     """``collective_mode = "single_process_multi_thread"``: one process driving all local GPUs with per-grad
     allreduce (transpiler/collective.py:421-470).  Here every GPU has its own process; the sync mode is the
     same per-step allreduce."""
+
+
+class MultiThread(GradAllReduce):
+    """The "box" transpiler (transpiler/collective.py:434-740): ``trans_mode`` = ``all_reduce`` (one
+    ``c_allreduce_sum`` per gradient), ``fuse_all_reduce`` (gradients coalesced in groups of 128 first) or
+    ``all_gather`` (every GPU gathers all gradients and applies them).  All three give every replica the mean
+    gradient per step; the flat gradient buffer here is always "fused", so they map to the same sync mode."""
+
+    def __init__(self, nrings: int = 1, trans_mode: str = "all_reduce"):
+        if trans_mode not in ("all_reduce", "fuse_all_reduce", "all_gather"):
+            raise ValueError(f"unknown trans_mode {trans_mode!r}")
+        super().__init__(nrings, fuse_all_reduce=trans_mode != "all_reduce")
+        self.trans_mode = trans_mode
+        self.fuse_grad_size_in_num = 128
+
+
+Collective = GradAllReduce      # the transpilers' common base (transpiler/collective.py:36-255)
 
 
 class DistributeTranspilerConfig:
