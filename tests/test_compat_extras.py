@@ -437,6 +437,31 @@ def test_examples_run_on_cpu(tmp_path):
     assert len(ls) == 3 and ls[-1] < ls[0]
 
 
+def test_online_training_example_trains_days_and_resumes(tmp_path):
+    import subprocess
+    import sys
+    import os
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")}
+    out = str(tmp_path / "job")
+    cmd = [sys.executable, os.path.join(root, "examples", "online_train.py"), "--cpu", "--out", out, "--lines", "256"]
+    r = subprocess.run(cmd + ["--days", "20240101,20240102"], capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    first = [float(x.split("auc=")[1]) for x in r.stdout.split("summary:")[1].splitlines()[0].split()]
+    assert len(first) == 4 and first[-1] > first[0]
+    assert len(open(os.path.join(out, "donefile.txt")).read().strip().splitlines()) == 2
+    assert len(open(os.path.join(out, "xbox_patch_done.txt")).read().strip().splitlines()) == 4
+    assert os.path.isdir(os.path.join(out, "20240102", "0", "dense")) and os.path.isdir(os.path.join(out, "20240101", "base"))
+    # second run: finds the last batch model, skips the finished days, continues with the new one
+    r = subprocess.run(cmd + ["--days", "20240101,20240102,20240103"], capture_output=True, text=True, env=env, timeout=600)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "resume from" in r.stdout and "20240102/0/" in r.stdout
+    second = [x for x in r.stdout.split("summary:")[1].splitlines()[0].split()]
+    assert [x.split(":")[0] for x in second] == ["20240103/1", "20240103/2"]
+    assert float(second[0].split("auc=")[1]) > first[0]            # it did not start from scratch
+    assert len(open(os.path.join(out, "donefile.txt")).read().strip().splitlines()) == 3
+
+
 def test_psgpu_wrapper_pybind_names(tmp_path):
     import torch
     from paddlebox_b200.box_wrapper import BoxWrapper
