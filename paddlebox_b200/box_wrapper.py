@@ -456,16 +456,27 @@ class BoxWrapper:
             if m.metric_phase == self._phase:
                 m.add_data(tensors)
 
+    def _metric_group(self):
+        """The process group metrics are reduced over: this wrapper's group, the default (world) group when none
+        was given — ``None`` means "one process, nothing to reduce" to the metric classes, so a multi-rank
+        wrapper must never hand them ``None``."""
+        if self.world_size <= 1:
+            return None
+        if self.group is not None:
+            return self.group
+        import torch.distributed as dist
+        return dist.group.WORLD if dist.is_available() and dist.is_initialized() else None
+
     def get_metric_msg(self, name: str) -> list:
         """[auc, bucket_error, mae, rmse, actual_ctr, predicted_ctr, copc, size]; reduces over
         the data-parallel group and resets the metric (box_wrapper.cc:1027-1046)."""
-        return self._metrics[name].get_metric_msg(self.group if self.world_size > 1 else None)
+        return self._metrics[name].get_metric_msg(self._metric_group())
 
     def get_continue_metric_msg(self, name: str) -> list:
         """[mae, rmse, actual value, predicted value, size] of a continuous-value metric
         (``GetContinueMetricMsg``, box_wrapper.cc:1048-1065); resets it."""
         m = self._metrics[name]
-        grp = self.group if self.world_size > 1 else None
+        grp = self._metric_group()
         if hasattr(m, "get_continue_msg"):
             return m.get_continue_msg(grp)
         msg = m.get_metric_msg(grp)

@@ -288,17 +288,19 @@ class CTRTrainer:
     def _deal_batches(self, dataset) -> int:
         """Deals the loaded records into batches and returns the worker index to iterate.
 
-        One process per GPU: ``set_rank_world`` already gave this process only its own share of the
-        files (data_set.cc:1963-1975), so ALL local records belong to this rank: they are dealt to a
-        single local worker, and the batch count is equalised across ranks with an allreduce(max)
-        (data_set.cc:2708-2750) so that every rank enters the in-kernel barriers of pull / push the
-        same number of times.  Several workers inside one process (``world`` readers over one
-        in-memory dataset) keep the round-robin deal."""
-        sharded = self.world > 1 and getattr(dataset, "_world", 1) == self.world
-        if not sharded:
+        One process per GPU: whatever this process loaded is ITS share of the pass — the files were split
+        between the processes before loading, by ``set_rank_world`` (round-robin, data_set.cc:1963-1975) or by
+        the job script (``fleet.util.get_file_shard`` / ``split_files``, the usual idiom).  So ALL local records
+        are dealt to a single local worker, and the batch count is equalised across ranks with an
+        allreduce(max) (data_set.cc:2708-2750) so that every rank enters the in-kernel barriers of pull / push
+        the same number of times.  Only a dataset the caller has explicitly dealt to several workers
+        (``prepare_train(n > 1, ...)``: several readers of one in-memory dataset) keeps that deal."""
+        if dataset._prepared_workers > 1:
+            return self.rank if dataset._prepared_workers == self.world else 0
+        if self.world == 1:
             if dataset._prepared_workers == 0:
-                dataset.prepare_train(self.world, self.rank)
-            return self.rank if dataset._prepared_workers > 1 else 0
+                dataset.prepare_train(1, 0)
+            return 0
         from .parallel.cluster import OP_MAX, Cluster
         dataset.prepare_train(1, 0)
         local = dataset.num_batches(0)

@@ -645,3 +645,33 @@ def cpu_queue_dataset_streaming_two_ranks(rank, world, data_dir):
     assert all(torch.allclose(gathered[0], t) for t in gathered)      # dense replicas stayed in step
     BoxWrapper.reset_instance()
     return {"steps": st["steps"], "instances": st["instances"]}
+
+
+def cpu_user_sharded_files_and_global_metrics(rank, world, data_dir):
+    """The job-script idiom: every rank takes its files with ``fleet.util.get_file_shard`` (no set_rank_world) and
+    reads metrics through the wrapper.  Every rank must train ALL the records it loaded, and the metric must
+    cover the records of all ranks."""
+    from paddlebox_b200 import fleet
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    from paddlebox_b200.dataset import DatasetFactory
+    from paddlebox_b200.models.ctr import CtrDnn
+    from paddlebox_b200.trainer import CTRTrainer, TrainerConfig
+    from tests.util_data import slot_vars
+    fleet.init()
+    files = sorted(os.path.join(data_dir, f) for f in os.listdir(data_dir) if f.startswith("part-"))
+    box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=rank, world_size=world)
+    box.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0})
+    box.init_metric("AucCalculator", "auc", "label", "pred", metric_phase=1, bucket_size=10000)
+    ds = DatasetFactory().create_dataset("PadBoxSlotDataset")
+    ds.set_use_var(slot_vars(3, 2)); ds.set_batch_size(10); ds.set_thread(1)
+    ds.set_filelist(fleet.util.get_file_shard(files))
+    ds.load_into_memory()
+    local = ds.get_memory_data_size()
+    torch.manual_seed(0)
+    tr = CTRTrainer(CtrDnn(num_slots=3, embedx_dim=4, dense_dim=2, hidden=(8,)), box, TrainerConfig())
+    ds.begin_pass()
+    st = tr.train_from_dataset(ds)
+    ds.end_pass(False)
+    size = box.get_metric_msg("auc")[7]
+    BoxWrapper.reset_instance()
+    return {"local": local, "trained": st["instances"], "metric_size": int(size), "steps": st["steps"]}

@@ -132,6 +132,16 @@ def test_queue_dataset_streams_on_two_ranks_with_unequal_shares(tmp_path):
     assert outs[0]["steps"] == outs[1]["steps"] == 8 and outs[1]["instances"] == 80
 
 
+def test_user_sharded_file_lists_train_everything_and_metrics_are_global(tmp_path):
+    from tests.util_data import write_files
+    write_files(str(tmp_path), n_files=4, lines_per_file=40, n_sparse=3, n_dense=2, key_space=60)
+    outs = _spawn(W.cpu_user_sharded_files_and_global_metrics, 2, "gloo", args=(str(tmp_path),))
+    for o in outs:
+        assert o["local"] == 80 and o["trained"] == 80, o          # every local record, not 1 / world of them
+        assert o["metric_size"] == 160, o                          # reduced over both ranks
+    assert outs[0]["steps"] == outs[1]["steps"] == 8
+
+
 def test_legacy_record_global_shuffle_two_ranks_gloo():
     outs = _spawn(W.cpu_legacy_global_shuffle, 2, "gloo")
     assert outs[0]["total_before"] == outs[0]["total_after"] == 110 and all(o["owner_ok"] for o in outs)
