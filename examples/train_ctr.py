@@ -95,8 +95,12 @@ def main():
     manifest = ModelManifest(os.path.join(out, "donefiles"))        # what serving and a restarted job read
     aucs = []
     for p in range(a.passes):
-        files = write_pass_files(data_dir, n_files=2 * world, lines=a.lines, n_sparse=a.slots, n_dense=a.dense, seed=p,
-                                 key_space=a.key_space)
+        if rank == 0:                     # one writer; the others wait (a second writer would truncate files being read)
+            write_pass_files(data_dir, n_files=2 * world, lines=a.lines, n_sparse=a.slots, n_dense=a.dense, seed=p,
+                             key_space=a.key_space)
+        if world > 1:
+            torch.distributed.barrier()
+        files = [os.path.join(data_dir, f"part-{p:03d}-{f:05d}") for f in range(2 * world)]
         ds.set_filelist(files)
         ds.preload_into_memory()          # read + parse + collect keys while (in a real job) the previous pass trains
         ds.wait_preload_done()            # ... and route the keys to their owning ranks (feed pass)
