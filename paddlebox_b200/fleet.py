@@ -223,3 +223,94 @@ def distributed_optimizer(optimizer, strategy=None):
     inside the table, the dense part by ``CTRTrainer``'s flat optimizer configured from ``optimizer``."""
     from .optimizer import BoxPSOptimizer
     return optimizer if isinstance(optimizer, BoxPSOptimizer) else BoxPSOptimizer(optimizer)
+
+
+# ---- the remaining role / topology queries of fleet_base.py -------------------------------------------------
+def node_num() -> int:
+    """Number of nodes (machines) of the job: world size / processes per node (torchrun's LOCAL_WORLD_SIZE)."""
+    lw = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
+    return max(1, worker_num() // lw)
+
+
+def local_rank() -> int:
+    return int(os.environ.get("LOCAL_RANK", "0"))
+
+
+def local_device_ids() -> list:
+    """The device this process drives (one process per GPU)."""
+    return [torch.cuda.current_device()] if torch.cuda.is_available() else []
+
+
+def world_device_ids() -> list:
+    lw = max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1")))
+    return [[r % lw] for r in range(worker_num())]
+
+
+def worker_endpoints(to_string: bool = False):
+    """``host:port`` of every worker as far as this process knows them: the rendezvous address for rank 0 and
+    PADDLE_TRAINER_ENDPOINTS when the launcher exported it."""
+    eps = [e for e in os.environ.get("PADDLE_TRAINER_ENDPOINTS", "").split(",") if e]
+    if not eps:
+        eps = [f"{os.environ.get('MASTER_ADDR', '127.0.0.1')}:{os.environ.get('MASTER_PORT', '0')}"]
+    return ",".join(eps) if to_string else eps
+
+
+def server_num() -> int:
+    return 0               # no separate server processes: the table lives in the workers' HBM
+
+
+def server_index() -> int:
+    return 0
+
+
+def server_endpoints(to_string: bool = False):
+    return "" if to_string else []
+
+
+def is_coordinator() -> bool:
+    return False
+
+
+def run_server() -> None:
+    """See ``is_server``: nothing to run."""
+
+
+def distributed_model(model):
+    """Dygraph ``fleet.distributed_model``: the dense data-parallel wrapper.  Dense synchronisation is done by
+    ``CTRTrainer`` (flat gradient buffer, in-kernel or symmetric-memory allreduce), so the model is returned as is."""
+    return model
+
+
+def shrink(threshold=None) -> int:
+    """``fleet.shrink``: day-end table shrink with the table's configured thresholds."""
+    return shrink_sparse_table() if threshold is None else shrink_sparse_table(delete_after_unseen_days=float(threshold))
+
+
+def save(dirname: str, feed=(), fetch=(), mode: int = 0, trainer=None, **configs) -> int:
+    """``fleet.save``: the sparse table (``mode`` as in ``save_persistables``) and, with ``trainer``, its dense
+    persistables under ``<dirname>/dense``."""
+    n = save_persistables(None, dirname, mode=mode)
+    if trainer is not None and worker_index() == 0:
+        from . import checkpoint
+        checkpoint.save_persistables(trainer.model, os.path.join(dirname, "dense"), trainer.store)
+    barrier_worker()
+    return n
+
+
+def save_inference_model(executor=None, dirname: str = "", feeded_var_names=None, target_vars=None, main_program=None,
+                         export_for_deployment: bool = True, mode: int = 0, trainer=None) -> int:
+    """Serving model: the serving-format sparse base (xbox layout) plus the dense parameters — what
+    ``serving.Predictor`` loads."""
+    n = save_persistables(None, dirname, mode=2)
+    if trainer is not None and worker_index() == 0:
+        from . import checkpoint
+        checkpoint.save_persistables(trainer.model, os.path.join(dirname, "dense"))
+    barrier_worker()
+    return n
+
+
+def _get_heter_file_shard(self, files):
+    return self.get_file_shard(files)
+
+
+_Util.get_heter_file_shard = _get_heter_file_shard
