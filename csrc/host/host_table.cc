@@ -14,6 +14,8 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <mutex>
+#include <shared_mutex>
 #include <sstream>
 #include <unordered_map>
 
@@ -610,7 +612,11 @@ class HostTable {
   void run_sharded(const uint64_t* keys, int64_t n, ThreadPool* pool, F fn, bool may_create = false) {
     const size_t S = shards_.size();
     if (!pool || n < 4096) {
-      for (int64_t i = 0; i < n; ++i) fn(shards_[shard_of(keys[i])], i);
+      for (int64_t i = 0; i < n; ++i) {
+        const size_t q = shard_of(keys[i]);
+        std::lock_guard<std::mutex> g(mu_[q]);
+        fn(shards_[q], i);
+      }
       return;
     }
     // one parallel pass computes every key's shard, a counting sort groups the positions by shard, then
@@ -642,6 +648,7 @@ class HostTable {
     pool->parallel_range(S, [&](size_t qb, size_t qe, int) {
       for (size_t q = qb; q < qe; ++q) {
         Shard& shard = shards_[q];
+        std::lock_guard<std::mutex> g(mu_[q]);
         if (may_create) {            // one growth step instead of repeated doubling while rows are added
           size_t extra = (size_t)(start[q + 1] - start[q]);
           if (shard.rows.capacity() < shard.rows.size() + extra * L.stride)
@@ -656,7 +663,13 @@ class HostTable {
   }
   std::vector<Shard> shards_;
   std::vector<SsdShard> ssd_;
-  std::vector<std::mutex> mu_;
+  std::vector<std::mutex> mu_;       // one per shard: held while a bulk call walks that shard
+ public:
+  // Bulk calls (fetch / store / pull / push) hold this shared and lock the shards they walk, so several of
+  // them may run at once (the pass builder's fetch threads, a write-back next to the next pass's BuildPull);
+  // whole-table operations (save, load, shrink, spill, LoadSSD2Mem, clear, key export) hold it exclusively.
+  // Taken in the C entry points below.
+  mutable std::shared_mutex table_mu;
 };
 
 }  // namespace pbh
@@ -674,51 +687,61 @@ int pbh_table_create(void** out, int embedx_dim, int optimizer, const PbxSparseO
   return 0;
 }
 int pbh_table_destroy(void* h) { delete (HostTable*)h; return 0; }
-int64_t pbh_table_size(void* h) { return (int64_t)((HostTable*)h)->size(); }
+int64_t pbh_table_size(void* h) { std::unique_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu); return (int64_t)((HostTable*)h)->size(); }
 int pbh_table_set_config(void* h, const PbxSparseOptConfig* cfg) { ((HostTable*)h)->cfg = *cfg; return 0; }
 int pbh_table_set_test_mode(void* h, int on) { ((HostTable*)h)->test_mode = on != 0; return 0; }
 int pbh_table_set_serving_quant(void* h, float scale) { ((HostTable*)h)->serving_quant_scale = scale; return 0; }
-int pbh_table_clear(void* h) { ((HostTable*)h)->clear(); return 0; }
+int pbh_table_clear(void* h) { std::unique_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu); ((HostTable*)h)->clear(); return 0; }
 int pbh_table_fetch_rows(void* h, const uint64_t* keys, int64_t n, float* out, int create) {
+  std::shared_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu);
   ((HostTable*)h)->fetch_rows(keys, n, out, create != 0, table_pool());
   return 0;
 }
 int pbh_table_store_rows(void* h, const uint64_t* keys, int64_t n, const float* rows, int mark_dirty) {
+  std::shared_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu);
   ((HostTable*)h)->store_rows(keys, n, rows, mark_dirty != 0, table_pool());
   return 0;
 }
 int pbh_table_pull(void* h, const uint64_t* keys, int64_t n, float* out, int out_stride) {
+  std::shared_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu);
   ((HostTable*)h)->pull(keys, n, out, out_stride, table_pool());
   return 0;
 }
 int pbh_table_push(void* h, const uint64_t* keys, int64_t n, const float* push, int push_stride) {
+  std::shared_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu);
   ((HostTable*)h)->push(keys, n, push, push_stride, table_pool());
   return 0;
 }
 int64_t pbh_table_shrink(void* h, float decay, float delete_threshold, float delete_after_unseen_days) {
+  std::unique_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu);
   return ((HostTable*)h)->shrink(decay, delete_threshold, delete_after_unseen_days);
 }
 int pbh_table_save(void* h, const char* dir, int mode, int part_shard_base, float base_threshold,
                    float delta_threshold, int clear_dirty, int64_t* n_saved) {
+  std::unique_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu);
   return ((HostTable*)h)->save(dir, mode, part_shard_base, base_threshold, delta_threshold, n_saved,
                                clear_dirty);
 }
 int pbh_table_load_file(void* h, const char* path, int serving, int64_t* n_loaded) {
+  std::unique_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu);
   return ((HostTable*)h)->load_file(path, serving != 0, n_loaded);
 }
 int pbh_table_load_file_owned(void* h, const char* path, int serving, int rank, int world, int64_t* n_loaded) {
+  std::unique_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu);
   return ((HostTable*)h)->load_file(path, serving != 0, n_loaded, rank, world);
 }
-int pbh_table_ssd_open(void* h, const char* dir) { return ((HostTable*)h)->ssd_open(dir); }
-int pbh_table_ssd_close(void* h, int unlink_files) { ((HostTable*)h)->ssd_close(unlink_files != 0); return 0; }
+int pbh_table_ssd_open(void* h, const char* dir) { std::unique_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu); return ((HostTable*)h)->ssd_open(dir); }
+int pbh_table_ssd_close(void* h, int unlink_files) { std::unique_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu); ((HostTable*)h)->ssd_close(unlink_files != 0); return 0; }
 int64_t pbh_table_spill(void* h, float min_unseen_days, int64_t max_mem_rows) {
+  std::unique_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu);
   return ((HostTable*)h)->spill(min_unseen_days, max_mem_rows, table_pool());
 }
-int64_t pbh_table_load_ssd2mem(void* h) { return ((HostTable*)h)->load_ssd2mem(table_pool()); }
-int64_t pbh_table_mem_rows(void* h) { return (int64_t)((HostTable*)h)->mem_rows(); }
-int64_t pbh_table_ssd_rows(void* h) { return (int64_t)((HostTable*)h)->ssd_rows(); }
+int64_t pbh_table_load_ssd2mem(void* h) { std::unique_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu); return ((HostTable*)h)->load_ssd2mem(table_pool()); }
+int64_t pbh_table_mem_rows(void* h) { std::unique_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu); return (int64_t)((HostTable*)h)->mem_rows(); }
+int64_t pbh_table_ssd_rows(void* h) { std::unique_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu); return (int64_t)((HostTable*)h)->ssd_rows(); }
 int64_t pbh_table_keys(void* h, uint64_t* out, int64_t max_n) {
   std::vector<uint64_t> ks;
+  std::unique_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu);
   ((HostTable*)h)->all_keys(&ks);
   int64_t n = std::min<int64_t>(max_n, (int64_t)ks.size());
   if (out && n > 0) memcpy(out, ks.data(), (size_t)n * 8);

@@ -205,6 +205,28 @@ int main(int argc, char** argv) {
     total += n0;
   }
   CHECK(total > 0 && total < (int64_t)uk.size() && pbh_table_size(tab2) == total);
+  // several bulk calls on ONE table at the same time (the pass builder's fetch threads; a write-back next to
+  // the next pass's BuildPull): shard locks inside the calls, a shared table lock around them
+  {
+    std::vector<std::thread> ths;
+    std::vector<uint64_t> ck(60000);
+    for (size_t i = 0; i < ck.size(); ++i) ck[i] = 7000000ull + (uint64_t)i * 3;
+    for (int t = 0; t < 4; ++t)
+      ths.emplace_back([&, t] {
+        const size_t n = ck.size() / 2, off = (size_t)t * (ck.size() / 8);
+        std::vector<float> r(n * (size_t)L.stride);
+        pbh_table_fetch_rows(tab, ck.data() + off, (int64_t)n, r.data(), 1);
+        if (t % 2) pbh_table_store_rows(tab, ck.data() + off, (int64_t)n, r.data(), 1);
+        std::vector<float> pl(n * 11);
+        pbh_table_pull(tab, ck.data() + off, (int64_t)n, pl.data(), 11);
+      });
+    std::atomic<int> bad_size{0};
+    ths.emplace_back([&] { for (int i = 0; i < 20; ++i) if (pbh_table_size(tab) <= 0) bad_size++; });
+    for (auto& th : ths) th.join();
+    CHECK(bad_size.load() == 0);
+    std::vector<float> r(ck.size() * (size_t)L.stride);
+    OK(pbh_table_fetch_rows(tab, ck.data(), (int64_t)ck.size(), r.data(), 0));
+  }
   // damaged model files: bytes knocked out, lines cut, fields removed -- loaded into fresh tables (a refusal
   // or a partial load are both fine; reading out of bounds is not)
   for (int round = 0; round < 16; ++round) {
