@@ -491,14 +491,19 @@ class HostTable {
   // mode 0 = all (batch model, full state), 1 = delta (dirty rows, serving format),
   //      2 = base (serving format: no optimizer state), 3 = batch model
   int save(const std::string& dir, int mode, int part_shard_base, float base_threshold, float delta_threshold,
-           int64_t* n_saved, int clear_dirty) {
-    int64_t total = 0;
-    for (size_t si = 0; si < shards_.size(); ++si) {
+           int64_t* n_saved, int clear_dirty, ThreadPool* pool = nullptr) {
+    // every shard writes its own file: the shards are saved in parallel over the pool
+    std::atomic<int64_t> total{0};
+    std::atomic<int> failed{-1};
+    auto save_shard = [&](size_t si) {
       Shard& s = shards_[si];
       char name[512];
       snprintf(name, sizeof(name), "%s/part-%03d-%05d", dir.c_str(), part_shard_base, (int)si);
       FILE* fp = fopen(name, "w");
-      PBH_REQUIRE(fp != nullptr, "cannot open %s for writing", name);
+      if (fp == nullptr) { failed.store((int)si); return; }
+      std::vector<char> iobuf(1 << 20);
+      setvbuf(fp, iobuf.data(), _IOFBF, iobuf.size());
+      int64_t n_rows = 0;
       // rows in host memory first, then the shard's cold rows straight from its SSD file (never dirty)
       std::vector<std::pair<uint64_t, uint64_t>> cold;
       if (!ssd_.empty() && mode != 1) cold.assign(ssd_[si].index.begin(), ssd_[si].index.end());
@@ -530,14 +535,19 @@ class HostTable {
           }
         }
         fputc('\n', fp);
-        ++total;
+        ++n_rows;
         // clear_dirty: 1 = a delta save clears the flags of the rows it wrote; 2 = so does a full save (mode 0
         // writes every row: the delta baseline is reset as a whole, what a base save wants)
         if (in_mem && ((clear_dirty && mode == 1) || (clear_dirty == 2 && mode == 0))) s.dirty[i] = 0;
       }
-      fclose(fp);
-    }
-    if (n_saved) *n_saved = total;
+      if (fclose(fp) != 0) failed.store((int)si);
+      total += n_rows;
+    };
+    const size_t S = shards_.size();
+    if (pool) pool->parallel_range(S, [&](size_t b, size_t e, int) { for (size_t i = b; i < e; ++i) save_shard(i); });
+    else for (size_t i = 0; i < S; ++i) save_shard(i);
+    PBH_REQUIRE(failed.load() < 0, "cannot write %s/part-%03d-%05d", dir.c_str(), part_shard_base, failed.load());
+    if (n_saved) *n_saved = total.load();
     return 0;
   }
 
@@ -567,6 +577,8 @@ class HostTable {
       size_t need = 5 + (serving ? 0 : L.embed_state) + 2;
       if (f.size() < need) continue;
       if (world > 1 && (int)((mix64(key) >> 40) % (uint64_t)world) != rank) continue;
+      // (several files may be loaded at once: the row is created and filled under its shard's lock)
+      std::lock_guard<std::mutex> shard_guard(mu_[shard_of(key)]);
       float* row = find_or_create(key, true);
       init_row(row, key);
       size_t q = 0;
@@ -720,14 +732,14 @@ int pbh_table_save(void* h, const char* dir, int mode, int part_shard_base, floa
                    float delta_threshold, int clear_dirty, int64_t* n_saved) {
   std::unique_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu);
   return ((HostTable*)h)->save(dir, mode, part_shard_base, base_threshold, delta_threshold, n_saved,
-                               clear_dirty);
+                               clear_dirty, table_pool());
 }
 int pbh_table_load_file(void* h, const char* path, int serving, int64_t* n_loaded) {
-  std::unique_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu);
+  std::shared_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu);      // (files may load concurrently: rows are filled under shard locks)
   return ((HostTable*)h)->load_file(path, serving != 0, n_loaded);
 }
 int pbh_table_load_file_owned(void* h, const char* path, int serving, int rank, int world, int64_t* n_loaded) {
-  std::unique_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu);
+  std::shared_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu);
   return ((HostTable*)h)->load_file(path, serving != 0, n_loaded, rank, world);
 }
 int pbh_table_ssd_open(void* h, const char* dir) { std::unique_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu); return ((HostTable*)h)->ssd_open(dir); }

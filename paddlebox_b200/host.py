@@ -124,15 +124,19 @@ class HostTable:
     def load(self, directory: str, serving: bool = False, rank: int = 0, world: int = 1) -> int:
         """Load every ``part-*`` file of ``directory``.  With ``world`` > 1 only the keys that rank ``rank``
         owns are kept, whatever number of ranks wrote the files (resharding on load)."""
-        total = 0
-        for name in sorted(os.listdir(directory)):
-            if not name.startswith("part-"):
-                continue
+        files = [os.path.join(directory, n) for n in sorted(os.listdir(directory)) if n.startswith("part-")]
+
+        def load_one(path: str) -> int:
             n = C.c_int64()
-            N.hcheck(N.host().pbh_table_load_file_owned(self._h, os.path.join(directory, name).encode(), int(serving),
-                                                        rank, world, C.byref(n)))
-            total += n.value
-        return total
+            N.hcheck(N.host().pbh_table_load_file_owned(self._h, path.encode(), int(serving), rank, world, C.byref(n)))
+            return n.value
+
+        if len(files) <= 1:
+            return sum(load_one(f) for f in files)
+        # the native call parses without the GIL and fills rows under shard locks: files load in parallel
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max_workers=min(16, len(files), (os.cpu_count() or 4))) as ex:
+            return sum(ex.map(load_one, files))
 
     # ---- SSD tier ----------------------------------------------------------------------------
     def ssd_open(self, directory: str) -> None:
