@@ -461,12 +461,16 @@ class HostTable {
   }
 
   // decay + evict (CtrDymfAccessor::Shrink); returns survivors
-  int64_t shrink(float decay, float delete_threshold, float delete_after_unseen_days) {
-    int64_t kept = 0;
-    load_ssd2mem(nullptr);        // decay and ageing apply to every row, cold ones included
-    for (auto& s : shards_) {
-      Shard ns;
-      for (size_t i = 0; i < s.keys.size(); ++i) {
+  int64_t shrink(float decay, float delete_threshold, float delete_after_unseen_days, ThreadPool* pool = nullptr) {
+    load_ssd2mem(pool);           // decay and ageing apply to every row, cold ones included
+    // shards in parallel; inside a shard the survivors are compacted in place (no second copy of the shard)
+    // and the index is rebuilt only when something was evicted
+    std::atomic<int64_t> kept{0};
+    auto shrink_shard = [&](size_t si) {
+      Shard& s = shards_[si];
+      const size_t n = s.keys.size();
+      size_t w = 0;
+      for (size_t i = 0; i < n; ++i) {
         float* row = s.rows.data() + i * L.stride;
         row[0] *= decay;
         row[1] *= decay;
@@ -474,15 +478,27 @@ class HostTable {
         float score = cfg.nonclk_coeff * (row[0] - row[1]) + cfg.clk_coeff * row[1];
         bool evict = s.keys[i] != 0 && (score < delete_threshold || row[L.off_tail + 2] > delete_after_unseen_days);
         if (evict) continue;
-        ns.index.emplace(s.keys[i], (uint32_t)ns.keys.size());
-        ns.keys.push_back(s.keys[i]);
-        ns.dirty.push_back(s.dirty[i]);
-        ns.rows.insert(ns.rows.end(), row, row + L.stride);
+        if (w != i) {
+          memmove(s.rows.data() + w * L.stride, row, L.stride * sizeof(float));
+          s.keys[w] = s.keys[i];
+          s.dirty[w] = s.dirty[i];
+        }
+        ++w;
       }
-      kept += (int64_t)ns.keys.size();
-      s = std::move(ns);
-    }
-    return kept;
+      if (w != n) {
+        s.keys.resize(w);
+        s.dirty.resize(w);
+        s.rows.resize(w * L.stride);
+        if (w * 2 < n) { s.rows.shrink_to_fit(); s.keys.shrink_to_fit(); s.dirty.shrink_to_fit(); }
+        s.index = FlatIndex();
+        for (size_t i = 0; i < w; ++i) s.index.emplace(s.keys[i], (uint32_t)i);
+      }
+      kept += (int64_t)w;
+    };
+    const size_t S = shards_.size();
+    if (pool) pool->parallel_range(S, [&](size_t b, size_t e, int) { for (size_t i = b; i < e; ++i) shrink_shard(i); });
+    else for (size_t i = 0; i < S; ++i) shrink_shard(i);
+    return kept.load();
   }
 
   // ---- text checkpoint, one directory per table, files part-<shard>-<file>
@@ -726,7 +742,7 @@ int pbh_table_push(void* h, const uint64_t* keys, int64_t n, const float* push, 
 }
 int64_t pbh_table_shrink(void* h, float decay, float delete_threshold, float delete_after_unseen_days) {
   std::unique_lock<std::shared_mutex> lk(((HostTable*)h)->table_mu);
-  return ((HostTable*)h)->shrink(decay, delete_threshold, delete_after_unseen_days);
+  return ((HostTable*)h)->shrink(decay, delete_threshold, delete_after_unseen_days, table_pool());
 }
 int pbh_table_save(void* h, const char* dir, int mode, int part_shard_base, float base_threshold,
                    float delta_threshold, int clear_dirty, int64_t* n_saved) {

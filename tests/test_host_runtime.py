@@ -624,3 +624,30 @@ def test_host_runtime_under_sanitizers(tmp_path):
     for mode in ("asan", "tsan"):
         log = (tmp_path / f"sanitizer_host_{mode}.log").read_text()
         assert "exit code 0" in log and "WARNING" not in log and "ERROR" not in log, log
+
+
+def test_shrink_compacts_in_place_and_keeps_survivors_intact():
+    """Half of the rows fall under the threshold: exactly they disappear, the survivors keep their rows
+    (aged by one day), lookups of the evicted keys miss."""
+    import torch
+    from paddlebox_b200.host import HostTable
+    t = HostTable(embedx_dim=8)
+    keys = np.arange(1, 60001, dtype=np.uint64)
+    t.fetch_rows(keys, create=True)
+    push = torch.zeros(keys.size, t.layout.push_stride)
+    push[:, 1] = torch.from_numpy((keys % 10).astype(np.float32))
+    push[:, 3:] = 0.5
+    t.push(keys, push)
+    before = t.fetch_rows(keys, create=False).copy()
+    cfg = t.config
+    score = cfg.nonclk_coeff * (before[:, 0] - before[:, 1]) + cfg.clk_coeff * before[:, 1]
+    kept = t.shrink(1.0, 0.45, 30.0)
+    want = keys[score >= 0.45]
+    assert 0 < want.size < keys.size and kept == want.size and t.size() == want.size
+    assert np.array_equal(np.sort(t.keys()), want)
+    b = before[score >= 0.45]
+    b[:, t.layout.off_tail + 2] += 1
+    assert np.allclose(t.fetch_rows(want, create=False), b)
+    assert t.size() == want.size                         # create=False lookups of evicted keys add nothing
+    gone = keys[score < 0.45][:100]
+    assert np.all(t.pull(gone).numpy() == 0)
