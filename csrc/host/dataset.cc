@@ -103,7 +103,7 @@ void KeySet::dump_sorted(std::vector<uint64_t>* out) const {
   out->reserve(cnt + 1);
   if (has_zero) out->push_back(0);
   for (uint64_t k : tab) if (k) out->push_back(k);
-  std::sort(out->begin(), out->end());
+  radix_sort_u64(*out);
 }
 
 void KeyAgent::flush_bucket(size_t s, std::vector<uint64_t>& b) {

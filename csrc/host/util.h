@@ -2,6 +2,7 @@
 // Reference roles: framework/channel.h:39-481 (ChannelObject), framework/threadpool.h
 // (ThreadPool, parallel_run_range), platform/timer.h.
 #pragma once
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
@@ -162,6 +163,29 @@ struct Timer {
   void pause() { total += std::chrono::duration<double>(clk::now() - t0).count(); }
   double seconds() const { return total; }
 };
+
+// In-place LSD radix sort of 64-bit keys (8-bit digits; a digit that is the same in every key costs one
+// counting pass and no move).  ~3x std::sort on random keys above a few thousand elements.
+inline void radix_sort_u64(std::vector<uint64_t>& v) {
+  const size_t n = v.size();
+  if (n < 4096) { std::sort(v.begin(), v.end()); return; }
+  std::vector<uint64_t> tmp(n);
+  uint64_t* src = v.data();
+  uint64_t* dst = tmp.data();
+  for (int shift = 0; shift < 64; shift += 8) {
+    size_t cnt[256] = {0};
+    for (size_t i = 0; i < n; ++i) ++cnt[(src[i] >> shift) & 255];
+    bool single = false;
+    for (int d = 0; d < 256; ++d) if (cnt[d] == n) { single = true; break; }
+    if (single) continue;
+    size_t pos[256];
+    size_t acc = 0;
+    for (int d = 0; d < 256; ++d) { pos[d] = acc; acc += cnt[d]; }
+    for (size_t i = 0; i < n; ++i) dst[pos[(src[i] >> shift) & 255]++] = src[i];
+    std::swap(src, dst);
+  }
+  if (src != v.data()) memcpy(v.data(), src, n * sizeof(uint64_t));
+}
 
 inline uint64_t mix64(uint64_t k) {
   k ^= k >> 33; k *= 0xff51afd7ed558ccdull; k ^= k >> 33; k *= 0xc4ceb9fe1a85ec53ull; k ^= k >> 33;
