@@ -519,37 +519,66 @@ int Dataset::read_file(const std::string& path) {
     piped = true;
   }
   if (!fp) return -1;
-  std::vector<char> iobuf(4 << 20);  // 4 MB buffered reads (BufferedLineFileReader)
-  setvbuf(fp, iobuf.data(), _IOFBF, iobuf.size());
+  // Block reads into one buffer, lines found with memchr and parsed in place (BufferedLineFileReader; no
+  // per-line copy).  Records come from a stash refilled from the pool 256 at a time (one lock per refill) and
+  // new ones get their value vectors reserved at the size the previous lines needed (a fresh vector would
+  // otherwise grow eight times per line).
+  std::vector<char> buf(4 << 20);
+  size_t have = 0;                    // bytes of an unfinished line carried to the front of the buffer
   std::mt19937_64 rng(mix64(std::hash<std::string>()(path)));
   std::uniform_real_distribution<float> uni(0.f, 1.f);
-  char* line = nullptr;
-  size_t cap = 0;
-  ssize_t len;
-  std::vector<SlotRecord*> block;
+  std::vector<SlotRecord*> block, stash;
   block.reserve(4096);
   int64_t feas = 0;
-  while ((len = getline(&line, &cap, fp)) > 0) {
-    if (sample_rate < 1.0f && uni(rng) > sample_rate) continue;  // Bernoulli sampling
+  size_t hint_u64 = 64, hint_f = 16;
+  auto next_record = [&]() -> SlotRecord* {
+    if (stash.empty()) pool_.get_many(256, &stash);
+    SlotRecord* r;
+    if (!stash.empty()) { r = stash.back(); stash.pop_back(); }
+    else r = new SlotRecord();
+    if (r->u64_vals.capacity() == 0) { r->u64_vals.reserve(hint_u64); r->f_vals.reserve(hint_f); }
+    return r;
+  };
+  SlotRecord* rec = nullptr;
+  auto handle_line = [&](const char* line, size_t len) {
+    if (sample_rate < 1.0f && uni(rng) > sample_rate) return;  // Bernoulli sampling
     lines_read_++;
-    SlotRecord* rec = pool_.get();
-    if (!parse_line(line, (size_t)len, rec)) {
-      lines_bad_++;
-      std::vector<SlotRecord*> one{rec};
-      pool_.put(one);
-      continue;
-    }
+    if (!rec) rec = next_record();
+    if (!parse_line(line, len, rec)) { lines_bad_++; return; }   // (the record is reused for the next line)
     feas += (int64_t)rec->u64_vals.size();
+    hint_u64 = std::max(hint_u64, rec->u64_vals.size());
+    hint_f = std::max(hint_f, rec->f_vals.size());
     block.push_back(rec);
+    rec = nullptr;
     if (block.size() >= 4096) {
       std::vector<SlotRecord*> out;
       out.swap(block);
       chan_.put(std::move(out));
       block.reserve(4096);
     }
+  };
+  for (;;) {
+    if (have == buf.size()) buf.resize(buf.size() * 2);          // a single line longer than the buffer
+    size_t got = fread(buf.data() + have, 1, buf.size() - have, fp);
+    size_t end = have + got;
+    const char* p = buf.data();
+    const char* e = p + end;
+    while (p < e) {
+      const char* nl = (const char*)memchr(p, '\n', (size_t)(e - p));
+      if (!nl) break;
+      handle_line(p, (size_t)(nl - p));
+      p = nl + 1;
+    }
+    have = (size_t)(e - p);
+    if (got == 0) {                                              // end of input: the last line may lack its newline
+      if (have) handle_line(p, have);
+      break;
+    }
+    if (have && p != buf.data()) memmove(buf.data(), p, have);
   }
+  if (rec) stash.push_back(rec);
+  if (!stash.empty()) pool_.put(stash);
   if (!block.empty()) chan_.put(std::move(block));
-  free(line);
   total_feasigns_ += feas;
   if (piped) pclose(fp); else fclose(fp);
   return 0;

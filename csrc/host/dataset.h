@@ -48,6 +48,11 @@ class RecordPool {
     }
     return new SlotRecord();
   }
+  // up to `want` pooled records under ONE lock (readers keep a small stash: no lock per line)
+  void get_many(size_t want, std::vector<SlotRecord*>* out) {
+    std::lock_guard<std::mutex> g(mu_);
+    while (want-- && !free_.empty()) { out->push_back(free_.back()); free_.pop_back(); }
+  }
   void put(std::vector<SlotRecord*>& rs) {
     std::lock_guard<std::mutex> g(mu_);
     for (auto* r : rs) {

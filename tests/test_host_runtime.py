@@ -651,3 +651,26 @@ def test_shrink_compacts_in_place_and_keeps_survivors_intact():
     assert t.size() == want.size                         # create=False lookups of evicted keys add nothing
     gone = keys[score < 0.45][:100]
     assert np.all(t.pull(gone).numpy() == 0)
+
+
+def test_reader_handles_block_boundaries_long_lines_and_missing_final_newline(tmp_path):
+    """The block reader carries unfinished lines across 4 MB reads, grows for a line longer than its buffer,
+    takes a last line without a newline, counts empty / damaged lines as bad, and keeps CRLF files readable."""
+    vars_ = slot_vars(2, 1)
+    # (label, dense 1, slot0, slot1); slot1 of the long line carries 600 000 ids: one line of ~5 MB > the 4 MB buffer
+    long_ids = " ".join(str(1000 + i) for i in range(600_000))
+    lines = [f"1 1 1 0.5 1 {10 + i} 2 {20 + i} {30 + i}" for i in range(200_000)]      # ~6 MB: crosses a block boundary
+    lines.insert(1234, "")                                                      # empty line
+    lines.insert(5000, "1 1 1 0.5 1")                                           # cut line
+    lines.insert(7777, f"1 0 1 0.25 1 7 600000 {long_ids}")
+    p = tmp_path / "big.txt"
+    p.write_text("\r\n".join(lines))                                            # CRLF, no newline at the end
+    d = _ds(vars_)
+    d.set_filelist([str(p)])
+    d.load_into_memory()
+    assert d.num_records() == 200_001
+    st = d.stats()
+    assert "lines=200003" in st and "bad_lines=2" in st, st
+    uk = set(d.unique_keys().tolist())
+    assert {0, 7, 10, 20, 30, 1000, 1000 + 599_999, 10 + 199_999, 30 + 199_999} <= uk
+    assert uk == {0, 7} | set(range(10, 601_000))                              # 10..200029 and the long line's 1000..600999
