@@ -5,7 +5,8 @@
 # preloaded because the interpreter itself is not instrumented.
 #   benchmarks/sanitize_pytests.sh [outdir] [pytest args...]      -> <outdir>/sanitizer_pytests_asan.log
 #   SAN=tsan benchmarks/sanitize_pytests.sh ...                   -> <outdir>/sanitizer_pytests_tsan.log
-# (tsan: tests that read through a pipe_command are left out -- the child shell would inherit the preload)
+# (tsan: tests that read through a pipe_command are left out -- the child shell would inherit the preload -- and so is
+#  the 5 MB-line reader test, whose shadow memory does not fit this container)
 set -u
 cd "$(dirname "$0")/.."
 OUT=${1:-profiles}
@@ -15,7 +16,7 @@ ARGS=${*:-tests/test_host_runtime.py tests/test_api_sweep.py tests/test_cpu_e2e.
 TMP=$(mktemp -d)
 SAN=${SAN:-asan}
 if [ $SAN = tsan ]; then
-  FL="-fsanitize=thread"; PRE=$(g++ -print-file-name=libtsan.so); KEXPR="not pipe_command"
+  FL="-fsanitize=thread"; PRE=$(g++ -print-file-name=libtsan.so); KEXPR="not pipe_command and not block_boundaries"
 else
   FL="-fsanitize=address,undefined -fno-sanitize-recover=undefined"
   PRE="$(g++ -print-file-name=libasan.so) $(g++ -print-file-name=libubsan.so)"; KEXPR=""
@@ -39,6 +40,6 @@ LOG=$OUT/sanitizer_pytests_$SAN.log
   [ "$ours" != "0" ] && cat $TMP/tsan_report.*
 } > $LOG 2>&1
 tail -4 $LOG
-rc=1; grep -q "exit code 0" $LOG && ! grep -q "[1-9][0-9]* stack frames inside libpbx_host" $LOG && rc=0
+rc=1; grep -q "exit code 0" $LOG && grep -q " passed" $LOG && ! grep -q "[1-9][0-9]* stack frames inside libpbx_host" $LOG && rc=0
 rm -rf $TMP
 exit $rc
