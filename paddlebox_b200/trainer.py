@@ -388,6 +388,67 @@ class CTRTrainer:
             self.dumper = None
 
 
+class FetchHandler:
+    """``fluid.executor.FetchHandler`` (executor.py:502-527): while ``train_from_dataset`` runs, ``handler`` is
+    called every ``period_secs`` with the current value of every variable of ``var_dict``.  A "variable" here is
+    the name of an entry of the model's output dict (``"pred"``, ``"loss"`` ...), a callable returning a tensor /
+    number, or a tensor; values arrive as numpy arrays (missing ones as ``None``)."""
+
+    def __init__(self, var_dict=None, period_secs: float = 60):
+        assert var_dict is not None
+        self.var_dict, self.period_secs = var_dict, period_secs
+
+    def handler(self, res_dict: dict) -> None:
+        import sys
+        for key, v in res_dict.items():
+            if hasattr(v, "reshape") and getattr(v, "size", 0):
+                sys.stdout.write(f"{key}[0]: {v.reshape(-1)[0]} ")
+        sys.stdout.write("\n")
+
+    @staticmethod
+    def help() -> None:
+        print("class MyHandler(FetchHandler):\n    def handler(self, res_dict):\n        print(res_dict['pred'][:4])\n"
+              "exe.train_from_dataset(model, dataset, fetch_handler=MyHandler(var_dict={'pred': 'pred'}, period_secs=30))")
+
+
+class _FetchHandlerMonitor:
+    """The reference's ``FetchHandlerMonitor`` (trainer_factory.py:88-170): a thread that wakes every
+    ``period_secs`` and hands the handler a snapshot."""
+
+    def __init__(self, trainer: "CTRTrainer", handler: FetchHandler):
+        import threading
+        self.trainer, self.handler = trainer, handler
+        self._stop = threading.Event()
+        self._thread = threading.Thread(target=self._loop, name="fetch-handler", daemon=True)
+
+    def snapshot(self) -> dict:
+        import numpy as np
+        outs = self.trainer.last_outputs or {}
+        res = {}
+        for name, var in self.handler.var_dict.items():
+            v = var() if callable(var) else outs.get(var) if isinstance(var, str) else var
+            if torch.is_tensor(v):
+                v = v.detach().float().cpu().numpy()
+            elif v is not None and not isinstance(v, np.ndarray):
+                v = np.asarray(v)
+            res[name] = v
+        return res
+
+    def _loop(self) -> None:
+        while not self._stop.wait(self.handler.period_secs):
+            try:
+                self.handler.handler(self.snapshot())
+            except Exception as e:  # noqa: BLE001  (a failing user handler must not end the training pass)
+                print(f"fetch handler failed: {e}")
+
+    def start(self) -> None:
+        self._thread.start()
+
+    def stop(self) -> None:
+        self._stop.set()
+        self._thread.join(timeout=10)
+
+
 class Executor:
     """``exe.train_from_dataset(program, dataset)`` facade: ``program`` is a model (or a
     prepared ``CTRTrainer``)."""
@@ -411,6 +472,13 @@ class Executor:
         tr.cfg.debug = tr.cfg.debug or debug
         tr.timers.enabled = tr.cfg.debug and torch.cuda.is_available()
         tr.cfg.is_test = False
+        if isinstance(fetch_handler, FetchHandler):
+            mon = _FetchHandlerMonitor(tr, fetch_handler)
+            mon.start()
+            try:
+                return tr.train_from_dataset(dataset)
+            finally:
+                mon.stop()
         return tr.train_from_dataset(dataset, print_period if fetch_handler else 0, fetch_handler)
 
     def infer_from_dataset(self, program, dataset, **kw):

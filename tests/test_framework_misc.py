@@ -642,3 +642,41 @@ def test_queue_dataset_streams_without_loading_the_pass(tmp_path):
         assert st["instances"] == 5 * 37 and st["steps"] >= 5 * 5
     finally:
         BoxWrapper.reset_instance()
+
+
+def test_fetch_handler_is_called_periodically_during_training(tmp_path):
+    import numpy as np
+    import torch
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    from paddlebox_b200.dataset import DatasetFactory
+    from paddlebox_b200.models.ctr import CtrDnn
+    from paddlebox_b200.trainer import CTRTrainer, Executor, FetchHandler, TrainerConfig
+    from tests.util_data import slot_vars, write_files
+    files = write_files(str(tmp_path), n_files=1, lines_per_file=600, n_sparse=3, n_dense=2, key_space=50)
+    BoxWrapper.reset_instance()
+    try:
+        box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=0, world_size=1)
+        box.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0})
+        ds = DatasetFactory().create_dataset("PadBoxSlotDataset")
+        ds.set_use_var(slot_vars(3, 2)); ds.set_batch_size(4); ds.set_thread(1); ds.set_filelist(files)
+        ds.load_into_memory(); ds.begin_pass()
+        tr = CTRTrainer(CtrDnn(num_slots=3, embedx_dim=4, dense_dim=2, hidden=(8,)), box, TrainerConfig())
+        seen = []
+
+        class H(FetchHandler):
+            def handler(self, res):
+                seen.append(res)
+                if len(seen) == 2:
+                    raise RuntimeError("a failing handler must not stop the pass")
+
+        st = Executor().train_from_dataset(tr, ds, fetch_handler=H({"p": "pred", "steps": lambda: tr.steps,
+                                                                   "nothing": "no_such_output"}, period_secs=0.02))
+        ds.end_pass(False)
+        assert st["instances"] == 600 and len(seen) >= 2
+        last = seen[-1]
+        assert isinstance(last["p"], np.ndarray) and last["p"].size == 4 and last["nothing"] is None
+        assert int(last["steps"]) > 0
+        FetchHandler({"a": 1}).handler({"a": np.array([3.0])})
+        FetchHandler.help()
+    finally:
+        BoxWrapper.reset_instance()
