@@ -491,3 +491,28 @@ class Executor:
         finally:
             self_box.set_test_mode(False)
             tr.cfg.is_test = False
+
+    def run(self, program=None, feed=None, fetch_list=None, return_numpy: bool = True, is_test: bool = False, **kw):
+        """``exe.run(program, feed=batch, fetch_list=[...])``: ONE step on one ``SlotBatch`` (training unless
+        ``is_test``); returns the fetched outputs in ``fetch_list`` order (``"loss"`` and the names of the model's
+        output dict), as numpy arrays by default.  A startup program (``program`` without a forward, or None) is
+        a no-op: parameters are initialised at construction."""
+        if program is None or feed is None or not (isinstance(program, CTRTrainer) or callable(program)):
+            return []
+        tr = self._trainer_for(program, **kw)
+        if is_test:
+            loss, outs = tr.infer_step(feed)
+        else:
+            loss = tr.train_step(feed)
+            outs = tr.last_outputs or {}
+        vals = []
+        for name in (fetch_list or []):
+            v = loss if name == "loss" else outs.get(name)
+            if return_numpy and torch.is_tensor(v):
+                v = v.detach().float().cpu().numpy()
+            vals.append(v)
+        return vals
+
+    def close(self) -> None:
+        """Release the trainers this executor created (the reference notifies its pservers here)."""
+        self._trainers.clear()
