@@ -13,6 +13,7 @@
 // the device.
 #include <algorithm>
 #include <cmath>
+#include <functional>
 #include <cstdio>
 #include <cstdlib>
 #include <unordered_map>
@@ -38,19 +39,22 @@ struct EdgeType {
     return (it != node_ids.end() && *it == id) ? (int64_t)(it - node_ids.begin()) : -1;
   }
 
-  void build() {
+  void build(ThreadPool* pool = nullptr) {
     node_ids = src;
     node_ids.insert(node_ids.end(), dst.begin(), dst.end());
-    std::sort(node_ids.begin(), node_ids.end());
+    radix_sort_u64(node_ids);
     node_ids.erase(std::unique(node_ids.begin(), node_ids.end()), node_ids.end());
     const size_t n = node_ids.size(), m = src.size();
     row_ptr.assign(n + 1, 0);
     std::vector<int64_t> si(m), di(m);
-    for (size_t e = 0; e < m; ++e) {
-      si[e] = index_of(src[e]);
-      di[e] = index_of(dst[e]);
-      ++row_ptr[si[e] + 1];
-    }
+    auto par = [&](size_t count, const std::function<void(size_t, size_t)>& fn) {
+      if (pool && count > 65536) pool->parallel_range(count, [&](size_t b, size_t e, int) { fn(b, e); });
+      else fn(0, count);
+    };
+    par(m, [&](size_t b, size_t e) {                       // id -> dense index, both ends of every edge
+      for (size_t k = b; k < e; ++k) { si[k] = index_of(src[k]); di[k] = index_of(dst[k]); }
+    });
+    for (size_t e = 0; e < m; ++e) ++row_ptr[si[e] + 1];
     for (size_t i = 0; i < n; ++i) row_ptr[i + 1] += row_ptr[i];
     col.assign(m, 0);
     const bool weighted = raw_w.size() == m && m > 0;
@@ -61,14 +65,17 @@ struct EdgeType {
       col[at] = di[e];
       if (weighted) wgt[at] = raw_w[e];
     }
-    for (size_t i = 0; i < n; ++i) {
-      const int64_t b = row_ptr[i], e2 = row_ptr[i + 1];
-      if (!weighted) { std::sort(col.begin() + b, col.begin() + e2); continue; }
-      std::vector<std::pair<int64_t, float>> tmp((size_t)(e2 - b));
-      for (int64_t j = b; j < e2; ++j) tmp[(size_t)(j - b)] = {col[j], wgt[j]};
-      std::sort(tmp.begin(), tmp.end());
-      for (int64_t j = b; j < e2; ++j) { col[j] = tmp[(size_t)(j - b)].first; wgt[j] = tmp[(size_t)(j - b)].second; }
-    }
+    par(n, [&](size_t nb, size_t ne) {                     // neighbour lists sorted by index, rows in parallel
+      std::vector<std::pair<int64_t, float>> tmp;
+      for (size_t i = nb; i < ne; ++i) {
+        const int64_t b = row_ptr[i], e2 = row_ptr[i + 1];
+        if (!weighted) { std::sort(col.begin() + b, col.begin() + e2); continue; }
+        tmp.resize((size_t)(e2 - b));
+        for (int64_t j = b; j < e2; ++j) tmp[(size_t)(j - b)] = {col[j], wgt[j]};
+        std::sort(tmp.begin(), tmp.end());
+        for (int64_t j = b; j < e2; ++j) { col[j] = tmp[(size_t)(j - b)].first; wgt[j] = tmp[(size_t)(j - b)].second; }
+      }
+    });
     src.clear(); src.shrink_to_fit();
     dst.clear(); dst.shrink_to_fit();
     raw_w.clear(); raw_w.shrink_to_fit();
@@ -178,7 +185,7 @@ int pbh_graph_load_edge_file(void* h, int type, const char* path, int reverse, i
 }
 
 int pbh_graph_build(void* h, int type) {
-  ((GraphStore*)h)->type(type).build();
+  ((GraphStore*)h)->type(type).build(graph_pool());
   return 0;
 }
 
