@@ -269,8 +269,14 @@ class PSGPUWrapper(BoxWrapper):
         if getattr(self, "table", None) is not None:
             self.table.set_config(cfg)
 
-    def init_gpu_server(self, conf: dict | None = None, **kw) -> None:
-        """``InitializeGPUServer``: sparse-SGD config from the fleet desc (ps_gpu_trainer.cc:137-254)."""
+    def init_gpu_server(self, conf: "dict | str | None" = None, **kw) -> None:
+        """``InitializeGPUServer``: sparse-SGD config from the fleet desc (ps_gpu_trainer.cc:137-254).  ``conf``:
+        a dict of ``SparseOptConfig`` names, or the job's ``fleet_desc`` protobuf text (``fleet_desc.py`` reads the
+        first sparse table's accessor out of it, as the reference does)."""
+        if isinstance(conf, str) and "downpour_table_param" in conf:
+            from .fleet_desc import sparse_config_from_fleet_desc
+            c, optimizer, _ = sparse_config_from_fleet_desc(conf)
+            conf = {**c, "optimizer": optimizer}
         self.initialize_gpu_and_load_model(conf or {}, **kw)
 
 

@@ -186,3 +186,82 @@ def test_pslib_style_fleet_calls_act_on_the_wrapper(tmp_path, box):
     assert torch.allclose(T.model[0].batch_size, before * 0.9)
     from paddlebox_b200.optimizer import BoxPSOptimizer
     assert isinstance(fleet.distributed_optimizer(object()), BoxPSOptimizer)
+
+
+FLEET_DESC = """
+# what a pslib job hands its trainers (server part only)
+server_param {
+  downpour_server_param {
+    downpour_table_param {
+      table_id: 0
+      table_class: "DownpourSparseTable"
+      shard_num: 1950
+      type: PS_SPARSE_TABLE
+      accessor {
+        accessor_class: "DownpourUnitAccessor"
+        fea_dim: 11
+        embedx_dim: 8
+        embedx_threshold: 5
+        downpour_accessor_param {
+          nonclk_coeff: 0.2
+          click_coeff: 2.0
+          base_threshold: 1.5
+          delta_threshold: 0.25
+          delta_keep_days: 16.0
+          show_click_decay_rate: 0.98
+          delete_threshold: 0.8
+          delete_after_unseen_days: 30
+        }
+        embed_sgd_param {
+          name: "adagrad"
+          adagrad { learning_rate: 0.05 initial_g2sum: 3.0 initial_range: 0.0001 weight_bounds: -10.0 weight_bounds: 10.0 }
+        }
+        embedx_sgd_param {
+          name: "adam"
+          adam { learning_rate: 0.001, initial_range: 1e-4; beta1_decay_rate: 0.9 beta2_decay_rate: 0.999 ada_epsilon: 1e-8
+                 weight_bounds: [-5.0, 5.0] }
+        }
+      }
+    }
+    downpour_table_param { table_id: 1 table_class: "DownpourDenseTable" type: PS_DENSE_TABLE
+      accessor { accessor_class: "DownpourDenseValueAccessor" dense_sgd_param { name: "adam" } fea_dim: 1234 } }
+    service_param { server_class: "DownpourBrpcPsServer" start_server_port: 0 }
+  }
+}
+trainer_param { dense_table { table_id: 1 dense_variable_name: "fc_0.w_0" dense_variable_name: "fc_0.b_0" } }
+"""
+
+
+def test_fleet_desc_text_gives_the_sparse_config():
+    from paddlebox_b200.fleet_desc import parse_text_format, sparse_config_from_fleet_desc
+    d = parse_text_format(FLEET_DESC)
+    tabs = d["server_param"]["downpour_server_param"]["downpour_table_param"]
+    assert len(tabs) == 2 and tabs[0]["type"] == "PS_SPARSE_TABLE" and tabs[0]["shard_num"] == 1950
+    assert d["trainer_param"]["dense_table"]["dense_variable_name"] == ["fc_0.w_0", "fc_0.b_0"]
+    conf, opt, extra = sparse_config_from_fleet_desc(FLEET_DESC)
+    assert opt == "adagrad" and extra == {"embedx_dim": 8}
+    assert conf == {"nonclk_coeff": 0.2, "clk_coeff": 2.0, "mf_create_thresholds": 5.0, "learning_rate": 0.05,
+                    "initial_range": 0.0001, "initial_g2sum": 3.0, "min_bound": -10.0, "max_bound": 10.0,
+                    "mf_learning_rate": 0.001, "mf_initial_range": 1e-4, "mf_beta1_decay_rate": 0.9,
+                    "mf_beta2_decay_rate": 0.999, "mf_ada_epsilon": 1e-8, "mf_min_bound": -5.0, "mf_max_bound": 5.0}
+    # the CTR accessors use one rule for embed and embedx
+    ctr = FLEET_DESC.replace("DownpourUnitAccessor", "DownpourCtrAccessor").replace(
+        "embed_sgd_param {", "sparse_sgd_param { learning_rate: 0.07 initial_g2sum: 2.0 initial_range: 0.001 "
+                             "weight_bounds: -1.0 weight_bounds: 1.0 }\n embed_sgd_param {")
+    c2, o2, _ = sparse_config_from_fleet_desc(ctr)
+    assert o2 == "adagrad" and c2["learning_rate"] == c2["mf_learning_rate"] == 0.07 and c2["mf_max_bound"] == 1.0
+    import pytest
+    with pytest.raises(ValueError):
+        sparse_config_from_fleet_desc("server_param { }")
+    with pytest.raises(ValueError):
+        parse_text_format("a { b: 1 ")
+    # and the wrapper takes the text as it is
+    from paddlebox_b200.ps_gpu import PSGPUWrapper
+    PSGPUWrapper.reset_instance()
+    try:
+        ps = PSGPUWrapper.set_instance(embedx_dim=8, device=torch.device("cpu"), rank=0, world_size=1)
+        ps.init_gpu_server(FLEET_DESC)
+        cfg = ps.host_table.config
+        assert abs(cfg.clk_coeff - 2.0) < 1e-6 and abs(cfg.mf_learning_rate - 0.001) < 1e-9 and abs(cfg.mf_create_thresholds - 5.0) < 1e-6
+    finally:
+        PSGPUWrapper.reset_instance()
