@@ -120,7 +120,11 @@ def save_persistables(executor=None, dirname: str = "", main_program=None, mode:
     3 = batch model (pslib :348-370).  Returns the rows this worker wrote."""
     box = _box()
     box._sync_to_host()
-    n = box.host_table.save(dirname, mode=0 if mode == 3 else mode, shard_base=box.rank, clear_dirty=(mode == 1))
+    n = box.host_table.save(dirname, mode=0 if mode == 3 else mode, shard_base=box.rank, clear_dirty=(mode == 1),
+                            base_threshold=float(kwargs.get("base_threshold", table_policy.get("base_threshold", 0.0)))
+                            if mode == 2 else 0.0,
+                            delta_threshold=float(kwargs.get("delta_threshold", table_policy.get("delta_threshold", 0.0)))
+                            if mode == 1 else 0.0)
     barrier_worker()
     return n
 
@@ -156,8 +160,14 @@ def load_one_table(table_id, model_path: str, mode: int = 0, **kwargs) -> int:
     return load_model(model_path, mode=mode)
 
 
-def shrink_sparse_table(decay: float = 0.98, delete_threshold: float = 0.0, delete_after_unseen_days: float = 30.0) -> int:
-    """Day-end decay of show / click and removal of stale rows (pslib :471-486); returns the rows removed here."""
+def shrink_sparse_table(decay: float | None = None, delete_threshold: float | None = None,
+                        delete_after_unseen_days: float | None = None) -> int:
+    """Day-end decay of show / click and removal of stale rows (pslib :471-486); returns the rows removed here.
+    Arguments left out take the job strategy's values (``distributed_optimizer``), else 0.98 / 0 / 30."""
+    decay = table_policy.get("show_click_decay_rate", 0.98) if decay is None else decay
+    delete_threshold = table_policy.get("delete_threshold", 0.0) if delete_threshold is None else delete_threshold
+    delete_after_unseen_days = table_policy.get("delete_after_unseen_days", 30.0) \
+        if delete_after_unseen_days is None else delete_after_unseen_days
     box = _box()
     box._sync_to_host()
     before = box.host_table.size()
@@ -217,11 +227,31 @@ def end_pass(scope=None) -> None:
     _box().end_pass()
 
 
+table_policy: dict = {}       # thresholds of the day-end calls, from the job's strategy (see distributed_optimizer)
+
+
 def distributed_optimizer(optimizer, strategy=None):
     """The reference wraps the optimizer into a ``DownpourOptimizer`` that rewrites the program for the PS
-    (pslib :281-294).  Here the wrapper's ``minimize`` only records the choice: the sparse part is optimized
-    inside the table, the dense part by ``CTRTrainer``'s flat optimizer configured from ``optimizer``."""
+    (pslib :281-294) and turns ``strategy`` into the fleet description (pslib/node.py).  Here the sparse part is
+    optimized inside the table and the dense part by ``CTRTrainer``'s flat optimizer configured from
+    ``optimizer``; a ``strategy`` dict with the pslib keys (``sparse_learning_rate``, ``sparse_embedx_threshold``,
+    ``sparse_delete_threshold`` ...) configures the wrapper's sparse optimizer (if the wrapper is initialised
+    already) and the thresholds ``shrink_sparse_table`` / ``save_persistables`` use by default."""
     from .optimizer import BoxPSOptimizer
+    if strategy:
+        from .fleet_desc import sparse_config_from_strategy
+        conf, kind, _, policy = sparse_config_from_strategy(dict(strategy))
+        table_policy.clear()
+        table_policy.update(policy)
+        table_policy["sparse_conf"] = {**conf, "optimizer": kind}
+        from .box_wrapper import BoxWrapper
+        box = BoxWrapper._instance
+        if box is not None and getattr(box, "host_table", None) is not None and kind == box.optimizer:
+            from . import _native as N
+            cfg = N.SparseOptConfig(**{**box.host_table.config.as_dict(), **conf})
+            box.host_table.set_config(cfg)
+            if getattr(box, "table", None) is not None:
+                box.table.set_config(cfg)
     return optimizer if isinstance(optimizer, BoxPSOptimizer) else BoxPSOptimizer(optimizer)
 
 

@@ -187,3 +187,50 @@ def sparse_config_from_fleet_desc(text: str | dict, table: int = 0):
     dim = acc.get("embedx_dim")
     extra = {"embedx_dim": int(dim)} if dim is not None else {}
     return conf, optimizer, extra
+
+
+def sparse_config_from_strategy(strategy: dict, prefix: str = ""):
+    """The ``strategy`` dict a pslib job gives ``fleet.distributed_optimizer(optimizer, strategy)`` (the reference
+    turns it into the fleet description, pslib/node.py:80-330) -> ``(SparseOptConfig keywords, optimizer kind,
+    {"embedx_dim": d}, table policy)``.  The table policy holds what the day-end calls use: ``base_threshold`` /
+    ``delta_threshold`` (which rows a serving base / delta contains), ``delete_threshold`` /
+    ``delete_after_unseen_days`` / ``show_click_decay_rate`` (shrink), ``ssd_unseenday_threshold`` (spill).
+    Defaults are the reference's."""
+    g = lambda k, d: strategy.get(prefix + k, d)        # noqa: E731
+    cls = g("sparse_accessor_class", "DownpourCtrAccessor")
+    wb = g("sparse_weight_bounds", None) or [-10, 10]
+    conf = {"nonclk_coeff": float(g("sparse_nonclk_coeff", 0.1)), "clk_coeff": float(g("sparse_click_coeff", 1)),
+            "mf_create_thresholds": float(g("sparse_embedx_threshold", 10))}
+    optimizer = "adagrad"
+    if cls in ("DownpourFeatureValueAccessor", "DownpourCtrAccessor", "DownpourCtrDymfAccessor",
+               "DownpourCtrDoubleAccessor"):
+        rule = {"learning_rate": float(g("sparse_learning_rate", 0.05)), "initial_g2sum": float(g("sparse_initial_g2sum", 3)),
+                "initial_range": float(g("sparse_initial_range", 1e-4)), "min_bound": float(wb[0]), "max_bound": float(wb[1])}
+        conf.update(rule)
+        conf.update({"mf_" + k: v for k, v in rule.items()})
+    elif cls in ("DownpourSparseValueAccessor", "DownpourUnitAccessor", "DownpourDoubleUnitAccessor"):
+        for pre, key_pre in (("", "embed_"), ("mf_", "embedx_")):
+            name = strategy.get(prefix + key_pre + "sparse_optimizer", g("sparse_optimizer", "adagrad"))
+            lr_default = 0.001 if name == "adam" else 0.05
+            sub = lambda k, d: strategy.get(prefix + key_pre + k, g(k, d))      # noqa: E731
+            b = sub("sparse_weight_bounds", None) or [-10, 10]
+            conf[pre + "learning_rate"] = float(sub("sparse_learning_rate", lr_default))
+            conf[pre + "initial_range"] = float(sub("sparse_initial_range", 1e-4))
+            conf[pre + "min_bound"], conf[pre + "max_bound"] = float(b[0]), float(b[1])
+            if name in ("adagrad", "std_adagrad"):
+                conf[pre + "initial_g2sum"] = float(sub("sparse_initial_g2sum", 3))
+            if name == "adam":
+                conf[pre + "beta1_decay_rate"] = float(sub("sparse_beta1_decay_rate", 0.9))
+                conf[pre + "beta2_decay_rate"] = float(sub("sparse_beta2_decay_rate", 0.999))
+                conf[pre + "ada_epsilon"] = float(sub("sparse_ada_epsilon", 1e-8))
+            if pre == "":
+                optimizer = {"naive": "adagrad", "std_adagrad": "adagrad"}.get(name, name)
+    else:
+        raise ValueError(f"strategy: sparse_accessor_class {cls!r} is not supported")
+    policy = {"base_threshold": float(g("sparse_base_threshold", 1.5)), "delta_threshold": float(g("sparse_delta_threshold", 0.25)),
+              "delta_keep_days": float(g("sparse_delta_keep_days", 16)),
+              "delete_after_unseen_days": float(g("sparse_delete_after_unseen_days", 30)),
+              "ssd_unseenday_threshold": float(g("sparse_ssd_unseenday_threshold", 1)),
+              "show_click_decay_rate": float(g("sparse_show_click_decay_rate", 0.98)),
+              "delete_threshold": float(g("sparse_delete_threshold", 0.8))}
+    return conf, optimizer, {"embedx_dim": int(g("sparse_embedx_dim", 8))}, policy

@@ -265,3 +265,30 @@ def test_fleet_desc_text_gives_the_sparse_config():
         assert abs(cfg.clk_coeff - 2.0) < 1e-6 and abs(cfg.mf_learning_rate - 0.001) < 1e-9 and abs(cfg.mf_create_thresholds - 5.0) < 1e-6
     finally:
         PSGPUWrapper.reset_instance()
+
+
+def test_pslib_strategy_configures_the_table_and_the_day_end_thresholds(box):
+    from paddlebox_b200 import fleet
+    from paddlebox_b200.fleet_desc import sparse_config_from_strategy
+    conf, kind, extra, policy = sparse_config_from_strategy({})
+    assert kind == "adagrad" and extra == {"embedx_dim": 8} and conf["learning_rate"] == 0.05 and conf["mf_create_thresholds"] == 10
+    assert policy["delete_threshold"] == 0.8 and policy["base_threshold"] == 1.5 and policy["show_click_decay_rate"] == 0.98
+    c2, k2, _, _ = sparse_config_from_strategy({"sparse_accessor_class": "DownpourUnitAccessor", "sparse_optimizer": "adagrad",
+                                               "embedx_sparse_optimizer": "adam", "embedx_sparse_learning_rate": 0.002,
+                                               "sparse_weight_bounds": [-2, 2]})
+    assert k2 == "adagrad" and c2["mf_learning_rate"] == 0.002 and c2["mf_beta2_decay_rate"] == 0.999 and c2["max_bound"] == 2.0
+    try:
+        fleet.distributed_optimizer(object(), {"sparse_learning_rate": 0.2, "sparse_click_coeff": 3, "sparse_delete_threshold": 2.5,
+                                               "sparse_show_click_decay_rate": 0.5, "sparse_base_threshold": 30.0})
+        assert abs(box.host_table.config.learning_rate - 0.2) < 1e-7 and abs(box.host_table.config.clk_coeff - 3.0) < 1e-7
+        _touch(box, range(1, 11), clicks=1.0)            # score = 0.1 * (3 - 1) + 3 * 1 = 3.2
+        _touch(box, range(11, 21), clicks=0.0)           # score = 0.1 * 3 = 0.3
+        # serving base keeps rows over the strategy's base threshold only (none reaches 30)
+        import tempfile
+        with tempfile.TemporaryDirectory() as d:
+            assert fleet.save_persistables(None, d + "/base", mode=2) == 0
+            assert fleet.save_persistables(None, d + "/base2", mode=2, base_threshold=1.0) == 10
+        # shrink with the strategy's decay 0.5 and delete threshold 2.5: scores become 1.6 and 0.15 -> all removed
+        assert fleet.shrink_sparse_table() == 20
+    finally:
+        fleet.table_policy.clear()
