@@ -264,7 +264,10 @@ class FleetUtil:
         box = self.box
         box._sync_to_host()
         # only a delta save moves the delta baseline (UpdateStatAfterSave, ctr_dymf_accessor.cc:151-175)
-        n = box.host_table.save(path, mode=0 if mode == 3 else mode, shard_base=box.rank, clear_dirty=(mode == 1))
+        pol = fleet.table_policy          # thresholds of the job's strategy (fleet.distributed_optimizer), else everything
+        n = box.host_table.save(path, mode=0 if mode == 3 else mode, shard_base=box.rank, clear_dirty=(mode == 1),
+                                base_threshold=float(pol.get("base_threshold", 0.0)) if mode == 2 else 0.0,
+                                delta_threshold=float(pol.get("delta_threshold", 0.0)) if mode == 1 else 0.0)
         if mode in (0, 3):
             self._save_dense(path)
         fleet.barrier_worker()
