@@ -518,6 +518,104 @@ class BoxWrapper:
         if self.use_cuda:
             torch.cuda.empty_cache()
 
+    # ---- the accessors ops and trainers of the reference read off the wrapper (box_wrapper.h:600-900) --------
+    def get_gpu_num(self) -> int:
+        """GPUs of this node that take part in the job (``GetGpuNum``)."""
+        import os
+        return max(1, int(os.environ.get("LOCAL_WORLD_SIZE", "1"))) if self.world_size > 1 else \
+            (1 if self.use_cuda else 0)
+
+    get_device_count = get_gpu_num
+
+    def get_mpi_rank(self) -> int:
+        """Rank of this NODE (``GetMpiRank``): the reference has one process per node."""
+        return self.rank // max(1, self.get_gpu_num()) if self.world_size > 1 else 0
+
+    def get_mpi_size(self) -> int:
+        return max(1, self.world_size // max(1, self.get_gpu_num()))
+
+    def get_nccl_rank_id(self, device_id: int | None = None) -> int:
+        """``mpi_rank * gpu_num + device_id`` (box_wrapper.h:448-450) = this process's rank."""
+        return self.rank if device_id is None else self.get_mpi_rank() * max(1, self.get_gpu_num()) + int(device_id)
+
+    def get_device_id(self) -> int:
+        return self.device.index if self.use_cuda and self.device.index is not None else 0
+
+    get_place_device_id = get_device_id
+
+    def get_round_id(self) -> int:
+        """Number of passes begun so far (``GetRoundId``)."""
+        cnt = getattr(self.timers, "count", None)
+        return int(cnt.get("begin_pass", 0)) if isinstance(cnt, dict) else int(getattr(self, "_round_id", 0))
+
+    def get_dataset_id(self) -> int:
+        return getattr(self, "_dataset_id", 0)
+
+    def get_slot_vector(self) -> list:
+        return list(getattr(self, "slot_vector", []))
+
+    def get_omited_slot(self) -> set:            # (sic)
+        return set(getattr(self, "slot_omit_in_feedpass", ()))
+
+    def get_lr_map(self) -> dict:
+        return dict(getattr(self, "lr_map", {}))
+
+    def get_expand_embed_dim(self) -> int:
+        return int(self.expand_embed_dim)
+
+    def get_feedpass_thread_num(self) -> int:
+        return int(FLAGS.pbx_pass_fetch_threads)
+
+    def gpu_mem_used(self) -> int:
+        """Bytes of HBM in use on this process's device (``GpuMemUsed``)."""
+        if not self.use_cuda:
+            return 0
+        free, total = torch.cuda.mem_get_info(self.device)
+        return int(total - free)
+
+    def use_afs_api(self) -> bool:
+        return getattr(self, "file_mgr", None) is not None
+
+    def get_file_mgr(self):
+        if getattr(self, "file_mgr", None) is None:
+            from .side_tables import BoxFileMgr
+            self.file_mgr = BoxFileMgr()
+        return self.file_mgr
+
+    def phase_num(self) -> int:
+        """2 when metrics are registered for both phases (join / update), else 1 (``PhaseNum``)."""
+        return 2 if len({m.metric_phase for m in self._metrics.values()}) > 1 else 1
+
+    def mode(self) -> int:
+        """1 in test mode, else 0 (``Mode``)."""
+        return int(bool(self._test_mode))
+
+    def get_q_tensor(self):
+        """The q-values stored by ``store_q_value`` in this step (``GetQTensor``)."""
+        from .ops.functional import stored_q_values
+        return stored_q_values()
+
+    def sync_dense(self, tensor, scale: float | None = None):
+        """``SyncDense``: the inter-node leg of the dense allreduce on ``tensor`` (the whole allreduce on CPU
+        worlds); sum over ranks, scaled by ``scale`` (default 1 / world)."""
+        if self.world_size == 1:
+            return tensor
+        import torch.distributed as dist
+        dist.all_reduce(tensor, group=self.group)
+        tensor.mul_(1.0 / self.world_size if scale is None else scale)
+        return tensor
+
+    @staticmethod
+    def execute_func(n: int, fn) -> None:
+        """``ExecuteFunc``: ``fn(i)`` for i < n over the host pool."""
+        from .parallel.cluster import execute_func
+        execute_func(n, fn)
+
+    @staticmethod
+    def exec_range_func(n: int, fn, parts: int | None = None) -> None:
+        from .parallel.cluster import exec_range_func
+        exec_range_func(n, fn, parts)
+
     def print_device_info(self) -> str:
         """``PrintDeviceInfo``: one line per visible device with its memory use."""
         lines = []
