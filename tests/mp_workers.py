@@ -675,3 +675,61 @@ def cpu_user_sharded_files_and_global_metrics(rank, world, data_dir):
     size = box.get_metric_msg("auc")[7]
     BoxWrapper.reset_instance()
     return {"local": local, "trained": st["instances"], "metric_size": int(size), "steps": st["steps"]}
+
+
+def cpu_preload_overlap_two_ranks(rank, world, data_dir):
+    """The production pipeline on several ranks: pass N+1 is read, parsed and fed (its keys routed to their
+    owners over the all-to-all) while pass N is between begin_pass and end_pass; ranks stay in step and every
+    key of every pass ends up on exactly one owner."""
+    from paddlebox_b200.box_wrapper import BoxWrapper, owner_of
+    from paddlebox_b200.dataset import DatasetFactory
+    from paddlebox_b200.models.ctr import CtrDnn
+    from paddlebox_b200.trainer import CTRTrainer, TrainerConfig
+    from tests.util_data import slot_vars, write_files
+    box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=rank, world_size=world)
+    box.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0})
+    box.init_metric("AucCalculator", "auc", "label", "pred", metric_phase=1, bucket_size=10000)
+    torch.manual_seed(0)
+    tr = CTRTrainer(CtrDnn(num_slots=3, embedx_dim=4, dense_dim=2, hidden=(8,)), box, TrainerConfig())
+    dss = []
+    for i in range(2):
+        ds = DatasetFactory().create_dataset("PadBoxSlotDataset")
+        ds.set_use_var(slot_vars(3, 2)); ds.set_batch_size(16); ds.set_thread(2)
+        ds.set_rank_world(rank, world)
+        dss.append(ds)
+
+    def files_for(p):
+        d = os.path.join(data_dir, f"p{p}")
+        if rank == 0:
+            os.makedirs(d, exist_ok=True)
+            write_files(d, n_files=2 * world, lines_per_file=48 + 16 * (p % 2), n_sparse=3, n_dense=2,
+                        key_space=50 + 10 * p, seed=p)
+        dist.barrier()
+        return sorted(os.path.join(d, f) for f in os.listdir(d))
+
+    cur = dss[0]
+    cur.set_filelist(files_for(0))
+    cur.set_date("20240101")
+    cur.preload_into_memory(); cur.wait_preload_done()
+    sizes, steps = [], []
+    for p in range(3):
+        nxt = dss[(p + 1) % 2]
+        cur.begin_pass()
+        nxt.set_filelist(files_for(p + 1))
+        nxt.preload_into_memory()
+        st = tr.train_from_dataset(cur)
+        nxt.wait_preload_done()                          # collective: keys of pass p+1 to their owners
+        cur.end_pass(False)
+        sizes.append(int(box.get_metric_msg("auc")[7]))
+        steps.append(st["steps"])
+        cur.release_memory()
+        cur = nxt
+    keys = box.host_table.keys()
+    assert np.all(owner_of(keys[keys != 0], world) == rank)
+    tot = torch.tensor([keys.size]); dist.all_reduce(tot)
+    flat = tr.store.flat.clone()
+    g = [torch.zeros_like(flat) for _ in range(world)]
+    dist.all_gather(g, flat)
+    assert all(torch.allclose(g[0], t) for t in g)
+    BoxWrapper.reset_instance()
+    return {"sizes": sizes, "steps": steps, "keys_total": int(tot)}

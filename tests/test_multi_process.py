@@ -142,6 +142,13 @@ def test_user_sharded_file_lists_train_everything_and_metrics_are_global(tmp_pat
     assert outs[0]["steps"] == outs[1]["steps"] == 8
 
 
+def test_next_pass_is_fed_while_the_current_one_trains_two_ranks(tmp_path):
+    outs = _spawn(W.cpu_preload_overlap_two_ranks, 2, "gloo", args=(str(tmp_path),))
+    assert outs[0] == outs[1]
+    # 4 files per pass of 48 / 64 / 48 lines: the metric covers both ranks' records
+    assert outs[0]["sizes"] == [4 * 48, 4 * 64, 4 * 48] and outs[0]["keys_total"] > 150
+
+
 def test_legacy_record_global_shuffle_two_ranks_gloo():
     outs = _spawn(W.cpu_legacy_global_shuffle, 2, "gloo")
     assert outs[0]["total_before"] == outs[0]["total_after"] == 110 and all(o["owner_ok"] for o in outs)
