@@ -16,16 +16,43 @@ from .parallel.cluster import OP_MAX, OP_MIN, OP_SUM, Cluster
 _cluster: Cluster | None = None
 
 
+_role_maker = None
+
+
 def init(role_maker=None, is_collective: bool = True, strategy=None, backend: str | None = None) -> None:
-    """Join the world described by the launcher's environment (RANK / WORLD_SIZE / MASTER_ADDR /
-    MASTER_PORT, as torchrun sets them); a single process needs no environment."""
-    global _cluster
+    """Join the job's world.  Without a role maker: the launcher's environment as torchrun sets it (RANK /
+    WORLD_SIZE / MASTER_ADDR / MASTER_PORT); a single process needs no environment.  With one
+    (``role_maker.py``: ``GeneralRoleMaker``, ``PaddleCloudRoleMaker`` ...): rank, world size and the rendezvous
+    address come from the Paddle launcher's variables it reads (``PADDLE_TRAINER_ID``, ``PADDLE_TRAINER_ENDPOINTS``,
+    ``TRAINING_ROLE``); a process launched as a parameter server joins nothing (there are no server processes)."""
+    global _cluster, _role_maker
+    import datetime
     import torch.distributed as dist
-    if not dist.is_initialized() and int(os.environ.get("WORLD_SIZE", "1")) > 1:
+    _role_maker = role_maker
+    rank, world, addr, port, timeout = None, None, None, None, None
+    if role_maker is not None:
+        role_maker.generate_role()
+        if role_maker.is_server():
+            _cluster = Cluster.ins()
+            return
+        rank, world = role_maker.worker_index(), role_maker.worker_num()
+        addr, port = role_maker.rendezvous()
+        timeout = getattr(role_maker, "_init_timeout_seconds", None)
+    else:
+        world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not dist.is_initialized() and world > 1:
         use_cuda = torch.cuda.is_available()
         if use_cuda:
-            torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", os.environ.get("RANK", "0"))))
-        dist.init_process_group(backend or ("nccl" if use_cuda else "gloo"))
+            torch.cuda.set_device(int(os.environ.get("LOCAL_RANK", os.environ.get("RANK", str(rank or 0)))) %
+                                  max(1, torch.cuda.device_count()))
+        kw = {}
+        if role_maker is not None:
+            if addr is None:
+                raise ValueError("the role maker knows no trainer endpoint to rendezvous at")
+            kw = {"init_method": f"tcp://{addr}:{port}", "rank": rank, "world_size": world}
+            if timeout:
+                kw["timeout"] = datetime.timedelta(seconds=min(int(timeout), 7 * 24 * 3600))
+        dist.init_process_group(backend or ("nccl" if use_cuda else "gloo"), **kw)
     _cluster = Cluster.ins()
 
 
@@ -46,11 +73,13 @@ def is_first_worker() -> bool:
 
 
 def is_worker() -> bool:
-    return True
+    return True if _role_maker is None else _role_maker.is_worker()
 
 
 def is_server() -> bool:
-    return False           # the parameter server lives inside the workers' GPUs
+    """False for every process that trains: the parameter server lives inside the workers' GPUs.  True only for
+    a process the launcher started with ``TRAINING_ROLE=PSERVER`` (it has nothing to do: ``run_server`` returns)."""
+    return False if _role_maker is None else _role_maker.is_server()
 
 
 def barrier_worker() -> None:

@@ -292,3 +292,44 @@ def test_pslib_strategy_configures_the_table_and_the_day_end_thresholds(box):
         assert fleet.shrink_sparse_table() == 20
     finally:
         fleet.table_policy.clear()
+
+
+def _free_port():
+    import socket
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+@pytest.mark.parametrize("kind", ["general", "collective"])
+def test_role_makers_join_the_world_from_the_paddle_launcher_environment(kind, tmp_path):
+    """Two trainer processes (and, for the PS-style role maker, one process launched as a parameter server) started
+    with the variables Paddle's launchers export; ``fleet.init(role_maker)`` joins them into one world."""
+    import subprocess
+    import sys
+    import json as _json
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    worker = os.path.join(root, "tests", "rm_worker.py")
+    eps = f"127.0.0.1:{_free_port()},127.0.0.1:{_free_port()}"
+    base = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK", "MASTER_ADDR", "MASTER_PORT")}
+    base.update({"PADDLE_TRAINER_ENDPOINTS": eps, "PADDLE_TRAINERS_NUM": "2", "PADDLE_PSERVERS_IP_PORT_LIST": "127.0.0.1:7001"})
+    procs = []
+    for r in range(2):
+        env = dict(base, PADDLE_TRAINER_ID=str(r), TRAINING_ROLE="TRAINER", PADDLE_TRAINING_ROLE="TRAINER")
+        procs.append(subprocess.Popen([sys.executable, str(worker), kind], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True))
+    if kind == "general":
+        env = dict(base, TRAINING_ROLE="PSERVER", POD_IP="127.0.0.1", PADDLE_PORT="7001")
+        procs.append(subprocess.Popen([sys.executable, str(worker), kind], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True))
+    outs = []
+    for p in procs:
+        so, se = p.communicate(timeout=300)
+        assert p.returncode == 0, se[-2000:]
+        outs.append(_json.loads(so.strip().splitlines()[-1]))
+    for r in range(2):
+        o = outs[r]
+        assert (o["rank"], o["world"], o["first"]) == (r, 2, r == 0) and o["sum"] == [3.0, 20.0] and o["gathered"] == [0, 1]
+        assert o["eps"] == eps.split(",")
+    if kind == "general":
+        assert outs[2] == {"server": 0}
