@@ -557,9 +557,6 @@ class BoxWrapper:
     def get_omited_slot(self) -> set:            # (sic)
         return set(getattr(self, "slot_omit_in_feedpass", ()))
 
-    def get_lr_map(self) -> dict:
-        return dict(getattr(self, "lr_map", {}))
-
     def get_expand_embed_dim(self) -> int:
         return int(self.expand_embed_dim)
 

@@ -126,3 +126,27 @@ def test_float_and_64_bit_scalars_are_wrapped_for_ctypes():
                         bad.append(f"{os.path.relpath(path, ROOT)}:{node.lineno}: {node.func.attr}({p}) <- {src}")
     assert seen > 100, seen
     assert not bad, "\n".join(bad)
+
+
+def test_no_method_is_defined_twice_in_a_class():
+    """A second ``def`` of the same name silently replaces the first (it did: ``BoxWrapper.get_lr_map``)."""
+    import ast
+    dup = []
+    for d, _, fs in os.walk(os.path.join(ROOT, "paddlebox_b200")):
+        for f in fs:
+            if not f.endswith(".py"):
+                continue
+            path = os.path.join(d, f)
+            for node in ast.walk(ast.parse(open(path).read(), path)):
+                if not isinstance(node, ast.ClassDef):
+                    continue
+                seen = {}
+                for b in node.body:
+                    if isinstance(b, (ast.FunctionDef, ast.AsyncFunctionDef)):
+                        deco = [ast.unparse(x) for x in b.decorator_list]
+                        if any(k in x for x in deco for k in ("setter", "property", "overload")):
+                            continue
+                        if b.name in seen:
+                            dup.append(f"{os.path.relpath(path, ROOT)}: {node.name}.{b.name} at lines {seen[b.name]} and {b.lineno}")
+                        seen[b.name] = b.lineno
+    assert not dup, "\n".join(dup)
