@@ -680,3 +680,31 @@ def test_fetch_handler_is_called_periodically_during_training(tmp_path):
         FetchHandler.help()
     finally:
         BoxWrapper.reset_instance()
+
+
+def test_run_cmd_and_stage_timers(tmp_path):
+    """``core.run_cmd`` of the reference's test_boxps.py (:96-106): output of a shell command, with retries
+    of a failing one until the time-out; and the host stage timers behind ``print_sync_timer``."""
+    import time
+    from paddlebox_b200.utils.shell import run_cmd
+    from paddlebox_b200.utils.timer import CudaStageTimers, StageTimers
+    assert run_cmd("echo hello").strip() == "hello"
+    assert run_cmd("ls /no/such/dir/at/all 2>/dev/null") == ""
+    flag = tmp_path / "flag"
+    # fails twice (no file), then succeeds: retried every 20 ms within the 2 s time-out
+    cmd = f"if [ -f {flag}.2 ]; then echo done; elif [ -f {flag}.1 ]; then touch {flag}.2; exit 1; else touch {flag}.1; exit 1; fi"
+    t0 = time.time()
+    assert run_cmd(cmd, time_out=2000, sleep_inter=20).strip() == "done" and time.time() - t0 < 2.0
+    t0 = time.time()
+    assert run_cmd("exit 3", time_out=150, sleep_inter=30) == "" and 0.1 < time.time() - t0 < 1.5
+    st = StageTimers()
+    with st.span("a"):
+        time.sleep(0.01)
+    st.add("b", 0.5)
+    st.add("b", 0.25)
+    assert st.count == {"a": 1, "b": 2} and abs(st.total["b"] - 0.75) < 1e-9 and st.total["a"] >= 0.009
+    assert "b=750.00ms/2" in st.report()
+    ct = CudaStageTimers(True)                       # no GPU here: a disabled timer costs nothing and reports nothing
+    with ct.span("x"):
+        pass
+    assert ct.summary() == {} or "x" in ct.summary()
