@@ -210,6 +210,11 @@ int pbh_dataset_load_into_memory(void* h) { return ((Dataset*)h)->load_into_memo
 int pbh_dataset_preload_into_memory(void* h) { return ((Dataset*)h)->preload_into_memory(); }
 int pbh_dataset_wait_preload_done(void* h) { return ((Dataset*)h)->wait_preload_done(); }
 int pbh_dataset_release_memory(void* h) { ((Dataset*)h)->release_memory(); return 0; }
+// record pool: records freed by release_memory are kept for the next pass up to a cap
+// (FLAGS_padbox_record_pool_max_size); trim returns them to the allocator now
+int64_t pbh_dataset_trim_record_pool(void* h) { return (int64_t)((Dataset*)h)->trim_record_pool(); }
+int64_t pbh_dataset_idle_records(void* h) { return (int64_t)((Dataset*)h)->idle_records(); }
+int pbh_dataset_set_record_pool_cap(void* h, int64_t cap) { ((Dataset*)h)->set_record_pool_cap((size_t)(cap < 0 ? 0 : cap)); return 0; }
 int pbh_dataset_local_shuffle(void* h, uint64_t seed) { ((Dataset*)h)->local_shuffle(seed); return 0; }
 int64_t pbh_dataset_merge_by_ins_id(void* h, int merge_size) { return ((Dataset*)h)->merge_by_ins_id(merge_size); }
 int pbh_dataset_slots_shuffle(void* h, const int* slots, int n, uint64_t seed) {

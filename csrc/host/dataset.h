@@ -61,6 +61,14 @@ class RecordPool {
     rs.clear();
   }
   size_t idle() { std::lock_guard<std::mutex> g(mu_); return free_.size(); }
+  // free every idle record (FLAGS_enable_force_mem_recyle / enbale_slotpool_auto_clear) / change the cap
+  size_t trim() {
+    std::vector<SlotRecord*> drop;
+    { std::lock_guard<std::mutex> g(mu_); drop.swap(free_); }
+    for (auto* r : drop) delete r;
+    return drop.size();
+  }
+  void set_cap(size_t cap) { std::lock_guard<std::mutex> g(mu_); cap_ = cap; }
  private:
   std::mutex mu_;
   std::vector<SlotRecord*> free_;
@@ -155,6 +163,9 @@ class Dataset {
   int save_partitioned(const std::string& prefix, int nparts, int mode, uint64_t seed) const;
   int load_archive(const std::string& path);
   std::string last_stats() const;
+  size_t trim_record_pool() { return pool_.trim(); }
+  size_t idle_records() { return pool_.idle(); }
+  void set_record_pool_cap(size_t cap) { pool_.set_cap(cap); }
 
   bool parse_line(const char* line, size_t len, SlotRecord* rec) const;
 

@@ -176,6 +176,10 @@ int pbh_dataset_set_reader_cores(void* ds, const int* cores, int n);
 int pbh_dataset_set_omit_slots(void* ds, const int* slot_indices, int n);
 /* feed configuration of src onto dst (not the file list, not rank / world): streaming readers keep several handles */
 int pbh_dataset_copy_config(void* dst, void* src);
+/* record pool (FLAGS_padbox_record_pool_max_size, enable_force_mem_recyle): idle records kept for the next pass */
+int64_t pbh_dataset_trim_record_pool(void* ds);
+int64_t pbh_dataset_idle_records(void* ds);
+int pbh_dataset_set_record_pool_cap(void* ds, int64_t cap);
 /* SSD tier (closed-library LoadSSD2Mem / CheckNeedLimitMem, fleet/box_wrapper.cc:1316-1324): cold rows
  * move to one append-only file per shard under `dir`; a lookup that misses host memory promotes the
  * row back.  spill: rows unseen for >= min_unseen_days (negative: ignore age), then — if

@@ -273,6 +273,8 @@ class BoxWrapper:
                 # bounded pinned chunks: D2H of chunk k+1 overlaps the host-table store of chunk k
                 self.last_pass_write_back = self.pass_builder(int(dk.numel())).write_back(dk, dr, mark_dirty=True)
         self._in_pass = False
+        if self.use_cuda and FLAGS.enable_force_hbm_recyle:          # cached device blocks back to the driver
+            torch.cuda.empty_cache()
         if need_save_delta and delta_path:
             self.save_delta(delta_path)
         if self._ssd and self.check_need_limit_mem():

@@ -479,7 +479,14 @@ class InMemoryDataset(DatasetBase):
         monitor.stat_set("STAT_total_feasign_num_in_mem", self._native.total_feasigns())
 
     def release_memory(self):
+        """Give the pass's records back.  They go to the native record pool for the next pass (up to
+        ``FLAGS.padbox_record_pool_max_size``); with ``FLAGS.enable_force_mem_recyle`` or
+        ``FLAGS.enbale_slotpool_auto_clear`` the pool is emptied, i.e. the memory returns to the allocator
+        (box_wrapper.cc:130-133, :178)."""
+        self._native.set_record_pool_cap(int(FLAGS.padbox_record_pool_max_size))
         self._native.release_memory()
+        if FLAGS.enable_force_mem_recyle or FLAGS.enbale_slotpool_auto_clear:
+            self._native.trim_record_pool()
         self._prepared_workers = 0
 
     def local_shuffle(self):

@@ -98,6 +98,17 @@ _d("pbx_pass_fetch_threads", 4, "CPU threads fetching host-table rows into pinne
 _d("pbx_dense_overlap_mb", 0.0, "> 0: the dense-gradient allreduce runs in buckets of this many MB, each started from an autograd hook as soon as its gradients are final, on a side stream under the rest of backward (large dense models; takes precedence over the fold)")
 _d("pbx_dense_overlap_bf16", False, "overlapped dense allreduce: gradients travel as bf16 (cast before, cast back + scale after)")
 _d("pbx_cpu_emulate_bf16", False, "CPU towers round every GEMM operand to bf16 (fp32 accumulation), the numerics of the GPU towers: for bf16-vs-fp32 training comparisons without a GPU")
+_d("dump_filed_same_as_aibox", False, "dump fields as 'name:v:v' with the name cut at its first '.', instead of 'name:count:v:v' (boxps_worker.cc:1801-1811)")
+_d("lineid_have_extend_info", False, "an instance id 'id<space>extra': the id leads the dump line, the extra part is appended as the last column (boxps_worker.cc:1783-1830)")
+_d("enable_print_dump_field_debug", False, "print every dumped field (name, width) while dumping")
+_d("enable_print_dump_info_debug", False, "print the number of dumped instances per batch")
+_d("enable_force_hbm_recyle", False, "end_pass returns cached device memory to the driver (box_wrapper.cc:198)")
+_d("enable_force_mem_recyle", False, "end of a pass releases the dataset's record pool to the OS (box_wrapper.cc:130)")
+_d("enbale_slotpool_auto_clear", False, "(sic) the record pool frees its idle records when a dataset releases its memory")
+_d("padbox_dataset_enable_unrollinstance", False, "the reference lets the parser plugin unroll loaded instances into several (data_set.cc:2275, ISlotParser::UnrollInstance); here a plugin emits as many records per input line as it wants at parse time (pbx_parse_file), so the flag is accepted and has nothing left to do")
+_d("gpugraph_load_node_list_into_hbm", True, "graph engine: node id lists are uploaded with the graph (upload_batch)")
+_d("graph_get_neighbor_id", False, "graph datasets also collect the neighbours' ids as pass keys (data_set.cc:532)")
+_d("enable_opt_get_features", False, "graph feed: features of sampled nodes are fetched in one batched call (data_feed.cu:371)")
 _d("pbx_fold_dense_allreduce", True, "data-parallel dense-gradient allreduce rides on the sparse push kernel's barriers")
 _d("pbx_sparse_dist", False, "GPU worlds: route pull/push through torch.distributed all-to-all (multi-node) instead of the one-node peer-memory engine; CPU worlds with > 1 rank always route this way")
 _d("pbx_sparse_cap_factor", 2.0, "mailbox capacity = factor * max_keys / nranks")

@@ -357,6 +357,15 @@ class NativeDataset:
     def release_memory(self):
         N.hcheck(N.host().pbh_dataset_release_memory(self._h))
 
+    def trim_record_pool(self) -> int:
+        return int(N.host().pbh_dataset_trim_record_pool(self._h))
+
+    def idle_records(self) -> int:
+        return int(N.host().pbh_dataset_idle_records(self._h))
+
+    def set_record_pool_cap(self, cap: int) -> None:
+        N.hcheck(N.host().pbh_dataset_set_record_pool_cap(self._h, C.c_int64(int(cap))))
+
     def local_shuffle(self, seed: int = 0):
         N.hcheck(N.host().pbh_dataset_local_shuffle(self._h, C.c_uint64(seed)))
 

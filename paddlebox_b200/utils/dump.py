@@ -10,6 +10,8 @@ import zlib
 
 import torch
 
+from ..flags import FLAGS
+
 
 class FieldDumper:
     def __init__(self, path: str, fields, dump_mode: int = 0, dump_interval: int = 10, num_threads: int = 1,
@@ -50,7 +52,6 @@ class FieldDumper:
             self._q.task_done()
 
     def _keep(self, lineid: str) -> bool:
-        from ..flags import FLAGS
         if FLAGS.padbox_dump_debug_lineid:                  # debug: only this line id (boxps_worker.cc:47-49)
             return lineid == FLAGS.padbox_dump_debug_lineid
         if self.mode == 0:
@@ -63,14 +64,26 @@ class FieldDumper:
     def dump_batch(self, ins_ids, tensors: dict):
         host = {k: tensors[k].detach().float().cpu().reshape(len(ins_ids), -1) for k in self.fields if k in tensors}
         lines = []
+        aibox, ext = FLAGS.dump_filed_same_as_aibox, FLAGS.lineid_have_extend_info
+        debug = FLAGS.enable_print_dump_field_debug
         for i, lid in enumerate(ins_ids):
             if not self._keep(lid):
                 continue
-            parts = [lid]
+            # FLAGS_lineid_have_extend_info: "id<space>extra" -> the id leads, the extra part closes the line
+            head, _, extra = lid.partition(" ") if ext else (lid, "", "")
+            parts = [head]
             for k, t in host.items():
                 row = t[i].tolist()
-                parts.append(f"{k}:{len(row)}:" + ":".join(f"{v:.6g}" for v in row))
+                # FLAGS_dump_filed_same_as_aibox: "name:v:v" with the name cut at its first '.', no count
+                name = k.split(".", 1)[0] if aibox else f"{k}:{len(row)}"
+                parts.append(name + ":" + ":".join(f"{v:.6g}" for v in row))
+                if debug:
+                    print(f"[dump] lineid=[{lid}] name={k} width={len(row)}", flush=True)
+            if ext and extra:
+                parts.append(extra)
             lines.append("\t".join(parts) + "\n")
+        if FLAGS.enable_print_dump_info_debug:
+            print(f"[dump] rank {self.rank}: dump ins count={len(lines)} of {len(ins_ids)}, fields={len(host)}", flush=True)
         if lines:
             self._q.put(lines)
 

@@ -202,3 +202,48 @@ def test_transpiler_and_optimizer_names():
         assert t.transpile(main_program=m) == mode
     assert cfg.sync_weight_step == 4 and cfg.sync_dense_mode == "kstep" and Collective is GradAllReduce
     assert LocalSGD.snapshot_name("w") == "w@SNAPSHOT"
+
+
+def test_dump_format_flags_and_record_pool_flags(tmp_path, capsys):
+    from paddlebox_b200.dataset import DatasetFactory
+    from paddlebox_b200.flags import set_flags
+    from paddlebox_b200.utils.dump import FieldDumper
+    ids = ["ins1 tagA", "ins2"]
+    outs = {"pred.tmp_0": torch.tensor([[0.25], [0.5]]), "label": torch.tensor([[1.0], [0.0]])}
+
+    def dump(flags):
+        set_flags(flags)
+        d = tmp_path / ("d" + "".join(str(int(v)) for v in flags.values()))
+        fd = FieldDumper(str(d), ["pred.tmp_0", "label"], 0, 1, 1, rank=0)
+        fd.dump_batch(ids, outs)
+        fd.close()
+        return sorted(open(os.path.join(d, f)).read() for f in os.listdir(d))[0].splitlines()
+
+    try:
+        plain = dump({"dump_filed_same_as_aibox": False, "lineid_have_extend_info": False})
+        assert plain == ["ins1 tagA\tpred.tmp_0:1:0.25\tlabel:1:1", "ins2\tpred.tmp_0:1:0.5\tlabel:1:0"]
+        aibox = dump({"dump_filed_same_as_aibox": True, "lineid_have_extend_info": True})
+        assert aibox == ["ins1\tpred:0.25\tlabel:1\ttagA", "ins2\tpred:0.5\tlabel:0"]
+        set_flags({"enable_print_dump_info_debug": True, "enable_print_dump_field_debug": True})
+        dump({"dump_filed_same_as_aibox": False, "lineid_have_extend_info": False})
+        out = capsys.readouterr().out
+        assert "dump ins count=2 of 2" in out and "name=label width=1" in out
+    finally:
+        set_flags({"dump_filed_same_as_aibox": False, "lineid_have_extend_info": False, "enable_print_dump_info_debug": False,
+                   "enable_print_dump_field_debug": False})
+    # record pool: released records are kept for the next pass, unless the recycle flags say otherwise
+    files = write_files(str(tmp_path / "data") if (tmp_path / "data").mkdir() is None else "", n_files=1, lines_per_file=50,
+                        n_sparse=2, n_dense=1, key_space=20)
+    ds = DatasetFactory().create_dataset("InMemoryDataset")
+    ds.set_use_var(slot_vars(2, 1)); ds.set_batch_size(8); ds.set_thread(1); ds.set_filelist(files)
+    ds.load_into_memory(); ds.release_memory()
+    assert ds._native.idle_records() == 50
+    try:
+        set_flags({"enable_force_mem_recyle": True})
+        ds.load_into_memory(); ds.release_memory()
+        assert ds._native.idle_records() == 0
+        set_flags({"enable_force_mem_recyle": False, "padbox_record_pool_max_size": 10})
+        ds.load_into_memory(); ds.release_memory()
+        assert ds._native.idle_records() == 10
+    finally:
+        set_flags({"enable_force_mem_recyle": False, "padbox_record_pool_max_size": 2000000})
