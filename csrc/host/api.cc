@@ -144,6 +144,7 @@ int pbh_dataset_set_int(void* h, const char* key, int64_t v) {
   else if (k == "parse_logkey") d->parse_logkey = v != 0;
   else if (k == "enable_pv_merge") d->enable_pv_merge = v != 0;
   else if (k == "collect_keys") d->collect_keys = v != 0;
+  else if (k == "record_reset_shrink") d->set_record_reset_shrink(v != 0);
   else if (k == "compact_batches") d->compact_batches = (int)v;
   else if (k == "compact_limit_mb") d->compact_limit_mb = (int64_t)v;
   else if (k == "parser_file_mode") d->parser_file_mode = v != 0;

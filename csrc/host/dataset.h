@@ -34,6 +34,13 @@ struct SlotRecord {
     search_id = 0; rank = cmatch = 0; ins_id.clear();
     u64_vals.clear(); u64_offs.clear(); f_vals.clear(); f_offs.clear();
   }
+  // reset that also gives the value buffers back (FLAGS_enable_slotrecord_reset_shrink, data_feed.h:211)
+  void reset_shrink() {
+    reset();
+    std::vector<uint64_t>().swap(u64_vals);
+    std::vector<float>().swap(f_vals);
+    std::string().swap(ins_id);
+  }
 };
 
 // Lock-protected free list with a capacity cap (FLAGS_padbox_record_pool_max_size).
@@ -56,7 +63,7 @@ class RecordPool {
   void put(std::vector<SlotRecord*>& rs) {
     std::lock_guard<std::mutex> g(mu_);
     for (auto* r : rs) {
-      if (free_.size() < cap_) { r->reset(); free_.push_back(r); } else delete r;
+      if (free_.size() < cap_) { if (shrink_on_reset) r->reset_shrink(); else r->reset(); free_.push_back(r); } else delete r;
     }
     rs.clear();
   }
@@ -69,6 +76,7 @@ class RecordPool {
     return drop.size();
   }
   void set_cap(size_t cap) { std::lock_guard<std::mutex> g(mu_); cap_ = cap; }
+  bool shrink_on_reset = false;
  private:
   std::mutex mu_;
   std::vector<SlotRecord*> free_;
@@ -166,6 +174,7 @@ class Dataset {
   size_t trim_record_pool() { return pool_.trim(); }
   size_t idle_records() { return pool_.idle(); }
   void set_record_pool_cap(size_t cap) { pool_.set_cap(cap); }
+  void set_record_reset_shrink(bool v) { pool_.shrink_on_reset = v; }
 
   bool parse_line(const char* line, size_t len, SlotRecord* rec) const;
 

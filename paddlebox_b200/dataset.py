@@ -484,6 +484,7 @@ class InMemoryDataset(DatasetBase):
         ``FLAGS.enbale_slotpool_auto_clear`` the pool is emptied, i.e. the memory returns to the allocator
         (box_wrapper.cc:130-133, :178)."""
         self._native.set_record_pool_cap(int(FLAGS.padbox_record_pool_max_size))
+        self._native.set("record_reset_shrink", int(FLAGS.enable_slotrecord_reset_shrink))
         self._native.release_memory()
         if FLAGS.enable_force_mem_recyle or FLAGS.enbale_slotpool_auto_clear:
             self._native.trim_record_pool()

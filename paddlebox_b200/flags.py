@@ -109,6 +109,10 @@ _d("padbox_dataset_enable_unrollinstance", False, "the reference lets the parser
 _d("gpugraph_load_node_list_into_hbm", True, "graph engine: node id lists are uploaded with the graph (upload_batch)")
 _d("graph_get_neighbor_id", False, "graph datasets also collect the neighbours' ids as pass keys (data_set.cc:532)")
 _d("enable_opt_get_features", False, "graph feed: features of sampled nodes are fetched in one batched call (data_feed.cu:371)")
+_d("enable_slotrecord_reset_shrink", False, "records returned to the pool also give their value buffers back (data_feed.h:211)")
+_d("enable_slotpool_wait_release", False, "the reference's pool may release records asynchronously and wait for it; release is synchronous here (accepted)")
+_d("padbox_slotpool_thread_num", 1, "threads of the reference's record pool; records are allocated by the reader threads here (accepted)")
+_d("enable_ins_parser_add_file_path", False, "whole-file parser plugins get the file path: always the case here (pbx_parse_file(path, ...)) (accepted)")
 _d("pbx_fold_dense_allreduce", True, "data-parallel dense-gradient allreduce rides on the sparse push kernel's barriers")
 _d("pbx_sparse_dist", False, "GPU worlds: route pull/push through torch.distributed all-to-all (multi-node) instead of the one-node peer-memory engine; CPU worlds with > 1 rank always route this way")
 _d("pbx_sparse_cap_factor", 2.0, "mailbox capacity = factor * max_keys / nranks")

@@ -150,3 +150,21 @@ def test_no_method_is_defined_twice_in_a_class():
                             dup.append(f"{os.path.relpath(path, ROOT)}: {node.name}.{b.name} at lines {seen[b.name]} and {b.lineno}")
                         seen[b.name] = b.lineno
     assert not dup, "\n".join(dup)
+
+
+def test_every_flag_of_the_reference_paddlebox_sources_exists():
+    """The FLAGS_* the reference's PaddleBox sources define or read (collected once from boxps worker / trainer,
+    data_set, data_feed, box_wrapper, ps_gpu_wrapper, heter_ps, metrics and the PaddleBox block of
+    platform/flags.cc) all exist here — wired, or accepted with the reason in their help text."""
+    from paddlebox_b200.flags import FLAGS
+    names = """padbox_record_pool_max_size padbox_slotpool_thread_num padbox_dataset_shuffle_thread_num
+    padbox_dataset_merge_thread_num padbox_dataset_disable_shuffle padbox_dataset_disable_polling
+    padbox_dataset_enable_unrollinstance padbox_auc_runner_mode padbox_dump_debug_lineid padbox_slotrecord_extend_dim
+    enable_pullpush_dedup_keys enable_pull_box_padding_zero use_gpu_replica_cache gpu_replica_cache_dim
+    enable_dense_nccl_barrier enable_sync_dense_moment enable_shuffle_by_searchid enable_binding_train_cpu
+    enable_ins_parser_file enable_ins_parser_add_file_path enable_dump_main_program enable_force_hbm_recyle
+    enable_force_mem_recyle enbale_slotpool_auto_clear enable_slotpool_wait_release enable_slotrecord_reset_shrink
+    enable_print_dump_field_debug enable_print_dump_info_debug dump_filed_same_as_aibox lineid_have_extend_info
+    enable_opt_get_features gpugraph_load_node_list_into_hbm graph_get_neighbor_id check_nan_inf""".split()
+    missing = [n for n in names if not hasattr(FLAGS, n)]
+    assert not missing, missing
