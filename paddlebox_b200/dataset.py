@@ -207,40 +207,75 @@ class DatasetBase:
         self.set_thread(thread_num)
 
     def set_data_feed_desc(self, desc: str):
-        """Configure from the text form of a ``DataFeedDesc`` (what ``desc()`` prints; the reference
-        passes the serialized proto, data_feed.proto:18-57): batch size, pipe command, threads, slots."""
-        import re
-        m = re.search(r"batch_size:\s*(\d+)", desc)
-        if m:
-            self.set_batch_size(int(m.group(1)))
-        m = re.search(r'pipe_command:\s*"([^"]*)"', desc)
-        if m:
-            self.set_pipe_command(m.group(1))
-        m = re.search(r"thread_num:\s*(\d+)", desc)
-        if m:
-            self.set_thread(int(m.group(1)))
+        """Configure from the protobuf TEXT form of a ``DataFeedDesc`` (data_feed.proto:18-57; what ``desc()``
+        prints and what the reference hands its native dataset): name, batch size, pipe command, threads, slots
+        (+ ``uid_slot``), ``rank_offset``, ``ads_offset``, ``pv_batch_size``, ``input_type``, ``so_parser_name``,
+        ``index_parser``, ``sample_rate``, ``graph_config``."""
+        from .fleet_desc import parse_text_format
+        d = parse_text_format(desc)
+        if "name" in d:
+            self.set_feed_type(str(d["name"]))
+        if "batch_size" in d:
+            self.set_batch_size(int(d["batch_size"]))
+        if "pipe_command" in d:
+            self.set_pipe_command(str(d["pipe_command"]))
+        if "thread_num" in d:
+            self.set_thread(int(d["thread_num"]))
+        msd = d.get("multi_slot_desc") or {}
+        raw = msd.get("slots", [])
+        raw = raw if isinstance(raw, list) else [raw]
         slots, used = [], []
-        for body in re.findall(r"slots\s*\{([^}]*)\}", desc):
-            f = dict(re.findall(r'(\w+):\s*"?([^\s"]+)"?', body))
-            is_float = f.get("type", "uint64") == "float"
-            dense = f.get("is_dense", "false").lower() == "true"
-            dim = int(f.get("shape", 1))
-            v = SlotVar(f["name"], "float32" if is_float else "int64", 0 if dense else 1, (-1, dim))
+        for f in raw:
+            is_float = str(f.get("type", "uint64")) == "float"
+            dense = bool(f.get("is_dense", False))
+            shape = f.get("shape", 1)
+            dim = int(shape[-1] if isinstance(shape, list) else shape)
+            v = SlotVar(str(f["name"]), "float32" if is_float else "int64", 0 if dense else 1, (-1, max(dim, 1)))
             slots.append(v)
-            if f.get("is_used", "true").lower() == "true":
+            if bool(f.get("is_used", False)):
                 used.append(v)
         if slots:
             self.set_use_var(used, slots)
+        if msd.get("uid_slot"):
+            self.set_uid_slot(str(msd["uid_slot"]))
+        for key, setter in (("rank_offset", "set_rank_offset"), ("ads_offset", "set_ads_offset"),
+                            ("pv_batch_size", "set_pv_batch_size"), ("input_type", "set_input_type"),
+                            ("so_parser_name", "set_so_parser_name"), ("index_parser", "set_index_parser"),
+                            ("sample_rate", "set_sample_rate"), ("graph_config", "set_graph_config")):
+            if key in d and hasattr(self, setter):
+                getattr(self, setter)(d[key])
 
     def desc(self) -> str:
-        """Text description of the feed configuration (``DataFeedDesc``, data_feed.proto:45-57)."""
-        lines = [f"name: \"{type(self).__name__}\"", f"batch_size: {self.batch_size}",
-                 f"pipe_command: \"{self.pipe_command}\"", f"thread_num: {self.thread_num}", "multi_slot_desc {"]
+        """Protobuf text of the feed configuration (``DataFeedDesc``, data_feed.proto:45-57); round-trips through
+        ``set_data_feed_desc``."""
+        q = lambda v: '"' + str(v).replace("\\", "\\\\").replace('"', '\\"') + '"'      # noqa: E731
+        b = lambda v: "true" if v else "false"                                                      # noqa: E731
+        lines = [f"name: {q(getattr(self, 'data_feed_type', None) or type(self).__name__)}", f"batch_size: {self.batch_size}",
+                 "multi_slot_desc {"]
         for s in self.all_slots:
             d = s.desc()
-            lines.append(f"  slots {{ name: \"{d['name']}\" type: \"{'float' if d['type'] else 'uint64'}\" "
-                         f"is_dense: {bool(d['is_dense'])} is_used: {bool(d['is_used'])} shape: {d['dim']} }}")
+            lines += ["  slots {", f"    name: {q(d['name'])}", f"    type: {q('float' if d['type'] else 'uint64')}",
+                      f"    is_dense: {b(d['is_dense'])}", f"    is_used: {b(d['is_used'])}", f"    shape: {d['dim']}", "  }"]
+        if getattr(self, "uid_slot", ""):
+            lines.append(f"  uid_slot: {q(self.uid_slot)}")
         lines.append("}")
+        lines += [f"pipe_command: {q(self.pipe_command)}", f"thread_num: {self.thread_num}"]
+        for key, attr in (("rank_offset", "rank_offset_name"), ("ads_offset", "ads_offset_name"),
+                          ("so_parser_name", "so_parser_name"), ("index_parser", "index_parser")):
+            if getattr(self, attr, ""):
+                lines.append(f"{key}: {q(getattr(self, attr))}")
+        if getattr(self, "pv_batch_size", None):
+            lines.append(f"pv_batch_size: {int(self.pv_batch_size)}")
+        if getattr(self, "input_type", None) is not None:
+            lines.append(f"input_type: {int(self.input_type)}")
+        if getattr(self, "sample_rate", None) not in (None, 1.0):
+            lines.append(f"sample_rate: {float(self.sample_rate)}")
+        gc = getattr(self, "graph_config", None)
+        if gc:
+            lines.append("graph_config {")
+            for k, v in gc.items():
+                lines.append(f"  {k}: {q(v) if isinstance(v, str) else (b(v) if isinstance(v, bool) else v)}")
+            lines.append("}")
         return "\n".join(lines)
 
     # ---- geometry ---------------------------------------------------------------------------
@@ -404,6 +439,7 @@ class InMemoryDataset(DatasetBase):
         return self._native.merge_by_ins_id(getattr(self, "merge_size", 0))
 
     def set_sample_rate(self, rate: float):
+        self.sample_rate = float(rate)
         self._native.set("sample_rate", float(rate))
 
     def set_queue_num(self, n: int):

@@ -797,3 +797,27 @@ def test_uid_slot_gives_the_user_id_of_every_instance(tmp_path):
         n0 = int(t[p]); p += 1 + n0
         want.append(int(t[p + 1]))
     assert uids.tolist() == want
+
+
+def test_data_feed_desc_text_round_trips():
+    import paddlebox_b200.dataset as D
+    from paddlebox_b200.dataset import dense_slot, sparse_slot
+    a = D.DatasetFactory().create_dataset("PadBoxSlotDataset")
+    a.set_use_var([dense_slot("label", 1), sparse_slot("s1")], [dense_slot("label", 1), dense_slot("d", 3), sparse_slot("s0"), sparse_slot("s1")])
+    a.set_batch_size(48); a.set_thread(6); a.set_pipe_command('awk "{print}"'); a.set_rank_offset("rank_offset"); a.set_ads_offset("ads")
+    a.set_pv_batch_size(12); a.set_input_type(1); a.set_sample_rate(0.5); a.set_uid_slot("s1"); a.set_feed_type("SlotPaddleBoxDataFeed")
+    a.set_graph_config({"walk_len": 8, "meta_path": "u2i-i2u", "gpu_graph_training": True})
+    text = a.desc()
+    assert 'name: "SlotPaddleBoxDataFeed"' in text and "is_used: false" in text and 'uid_slot: "s1"' in text
+    b = D.DatasetFactory().create_dataset("PadBoxSlotDataset")
+    b.set_data_feed_desc(text)
+    assert b.desc() == text
+    assert (b.batch_size, b.thread_num, b.pipe_command, b.rank_offset_name, b.pv_batch_size, b.input_type, b.sample_rate) == \
+        (48, 6, 'awk "{print}"', "rank_offset", 12, 1, 0.5)
+    assert [s.name for s in b.all_slots] == ["label", "d", "s0", "s1"] and [s.is_used for s in b.all_slots] == [True, False, False, True]
+    assert b.graph_config == {"walk_len": 8, "meta_path": "u2i-i2u", "gpu_graph_training": True}
+    # the one-line form older scripts print still parses
+    c = D.DatasetFactory().create_dataset("InMemoryDataset")
+    c.set_data_feed_desc('batch_size: 7 thread_num: 2 pipe_command: "cat" multi_slot_desc { slots { name: "x" type: "float" '
+                         'is_dense: true is_used: true shape: 4 } slots { name: "k" type: "uint64" is_used: true } }')
+    assert c.batch_size == 7 and c.dense_dim == 4 and c.num_sparse_slots == 1
