@@ -297,6 +297,12 @@ class BoxWrapper:
         self._cpu_unique = uk
         return vals, inv.to(torch.int32)
 
+    def push_grad_scale(self, batch_size: int) -> float:
+        """Factor applied to the embedding gradients of a push: ``-batch_size`` (the loss is a batch mean, the
+        sparse optimizer wants the per-instance sum, sign flipped for "descent"; PushCopy, box_wrapper.cu:344-416)
+        or ``-1`` when the trainer desc says ``scale_sparse_gradient_with_batch_size: false``."""
+        return -float(batch_size) if getattr(self, "scale_sparse_gradient_with_batch_size", True) else -1.0
+
     def push_sparse_grad(self, keys: torch.Tensor, restore: torch.Tensor, grads: torch.Tensor,
                          key2slot: torch.Tensor, batch_size: int) -> None:
         """Per-occurrence gradients [N, hidden] (show, clk counts in the first two columns)."""
@@ -305,24 +311,24 @@ class BoxWrapper:
         from .ops import reference as R
         if self.router is not None:
             n_unique = self.router._last[0].numel()
-            self.router.push(R.merge_push(restore, n_unique, grads, key2slot, 2, -float(batch_size)))
+            self.router.push(R.merge_push(restore, n_unique, grads, key2slot, 2, self.push_grad_scale(batch_size)))
             return
         if self.use_cuda:
             if FLAGS.pbx_deterministic_merge and self.world_size == 1:
                 # sorted, fp64 segmented merge (reference PushMergeCopy, box_wrapper.cu:417-475), then the plain
                 # by-key table update: bit-reproducible whatever the key skew
                 n_rows = self.engine.n_unique_rows
-                merged = R.merge_push_sorted(restore, n_rows, grads, key2slot, 2, -float(batch_size))
+                merged = R.merge_push_sorted(restore, n_rows, grads, key2slot, 2, self.push_grad_scale(batch_size))
                 uk = torch.zeros(n_rows, dtype=torch.int64, device=keys.device)
                 uk[restore.long()] = keys[:restore.numel()]
                 used = merged[:, 1] > 0                       # rows that received a show count
                 self.table.update(uk[used], merged[used].contiguous())
                 return
-            self.engine.push_keys(restore, grads.contiguous(), key2slot, 2, -float(batch_size))
+            self.engine.push_keys(restore, grads.contiguous(), key2slot, 2, self.push_grad_scale(batch_size))
             return
         uk = self._cpu_unique
         merge = R.merge_push_sorted if FLAGS.pbx_deterministic_merge else R.merge_push
-        merged = merge(restore, uk.numel(), grads, key2slot, 2, -float(batch_size))
+        merged = merge(restore, uk.numel(), grads, key2slot, 2, self.push_grad_scale(batch_size))
         self.host_table.push(uk.numpy(), merged)
 
     # ---- model save / load -------------------------------------------------------------------

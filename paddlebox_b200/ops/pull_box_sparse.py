@@ -216,7 +216,7 @@ class _SparseEmbeddingPool(torch.autograd.Function):
                 dout = dout.contiguous()
             # the pooled gradient is read in place from the (wider) input gradient: row stride = ld
             box.engine.push_pooled(ctx.restore, dout, cvm.contiguous(), batch.lod, B, S, Eo, 2,
-                                   attrs.dim_off(), -float(B), ld_dout=dout.stride(0))
+                                   attrs.dim_off(), box.push_grad_scale(B), ld_dout=dout.stride(0))
         else:
             dsp = dout[:, :ctx.sw].contiguous()
             dx = seqpool_cvm_backward(dsp, cvm, batch.lod, B, S, batch.N, attrs, box.hidden)

@@ -39,6 +39,45 @@ class TrainerConfig:
     dump_interval: int = 10
     dump_thread_num: int = 1
     is_test: bool = False
+    user_define_dump_filename: str = ""    # dump files are named part-<this>-<n> instead of part-<rank>-<n>
+    check_nan_var_names: list = field(default_factory=list)   # NaN / Inf check restricted to these outputs
+    loss_names: list = field(default_factory=list)
+    scale_sparse_gradient_with_batch_size: bool = True        # push scale -batch_size (True) or -1
+
+    @classmethod
+    def from_desc(cls, text: str) -> "TrainerConfig":
+        """From the protobuf text of a ``TrainerDesc`` (trainer_desc.proto:20-75, ``boxps_param`` :121-129): the
+        fields that mean something here — debug, dump_* (``enable_random_dump`` / ``random_with_lineid`` /
+        ``dump_interval`` choose the dump mode), ``check_nan_var_names``, ``loss_names``,
+        ``scale_sparse_gradient_with_batch_size``, and the BoxPS worker's ``async_mode`` / ``sync_dense_mode`` /
+        ``sync_weight_step`` / ``dump_thread_num``."""
+        from .fleet_desc import parse_text_format
+        d = parse_text_format(text)
+
+        def lst(v):
+            return [] if v is None else (list(v) if isinstance(v, list) else [v])
+        cfg = cls()
+        cfg.debug = bool(d.get("debug", False))
+        cfg.dump_fields = [str(x) for x in lst(d.get("dump_fields"))]
+        cfg.dump_param = [str(x) for x in lst(d.get("dump_param"))]
+        cfg.dump_fields_path = str(d.get("dump_fields_path", ""))
+        cfg.user_define_dump_filename = str(d.get("user_define_dump_filename", ""))
+        cfg.check_nan_var_names = [str(x) for x in lst(d.get("check_nan_var_names"))]
+        cfg.loss_names = [str(x) for x in lst(d.get("loss_names"))]
+        cfg.scale_sparse_gradient_with_batch_size = bool(d.get("scale_sparse_gradient_with_batch_size", True))
+        if bool(d.get("enable_random_dump", False)):
+            cfg.dump_mode = 1 if bool(d.get("random_with_lineid", False)) else 2
+            cfg.dump_interval = int(d.get("dump_interval", 10000))
+        bp = d.get("boxps_param") or {}
+        cfg.async_mode = bool(bp.get("async_mode", False))
+        cfg.sync_weight_step = int(bp.get("sync_weight_step", 1))
+        cfg.dump_thread_num = int(bp.get("dump_thread_num", 1))
+        mode = bp.get("sync_dense_mode", 0)
+        cfg.sync_dense_mode = "async" if cfg.async_mode else \
+            {0: "allreduce", 1: "kstep", 2: "allreduce"}.get(int(mode), "allreduce") if not isinstance(mode, str) else mode
+        if cfg.sync_weight_step > 1 and cfg.sync_dense_mode == "allreduce":
+            cfg.sync_dense_mode = "kstep"
+        return cfg
 
 
 class CTRTrainer:
@@ -84,7 +123,9 @@ class CTRTrainer:
         if self.cfg.dump_fields_path and (self.cfg.dump_fields or self.cfg.dump_param):
             from .utils.dump import FieldDumper
             self.dumper = FieldDumper(self.cfg.dump_fields_path, self.cfg.dump_fields, self.cfg.dump_mode,
-                                      self.cfg.dump_interval, self.cfg.dump_thread_num, rank=self.rank)
+                                      self.cfg.dump_interval, self.cfg.dump_thread_num, rank=self.rank,
+                                      user_filename=self.cfg.user_define_dump_filename)
+        self.box.scale_sparse_gradient_with_batch_size = bool(self.cfg.scale_sparse_gradient_with_batch_size)
         self.steps = 0
         self.last_outputs = None
         # data_norm(sync_stats): on GPUs of one node the three statistics vectors are reduced over the
@@ -278,7 +319,9 @@ class CTRTrainer:
         self.last_outputs = outs
         check = FLAGS.check_nan_inf if self.cfg.check_nan_inf is None else self.cfg.check_nan_inf
         if check:
-            check_batch_nan_inf({"loss": loss, **{k: v for k, v in outs.items() if torch.is_tensor(v)}},
+            names = set(self.cfg.check_nan_var_names)
+            check_batch_nan_inf({"loss": loss, **{k: v for k, v in outs.items()
+                                                  if torch.is_tensor(v) and (not names or k in names)}},
                                 self.cfg.dump_fields_path or None, tag=f"rank{self.rank}_step{self.steps}")
         self.box.add_metric_data(outs)           # AddAucMonitor
         if self.dumper is not None and self.cfg.dump_fields and batch.ins_ids is not None:

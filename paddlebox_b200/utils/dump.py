@@ -15,13 +15,14 @@ from ..flags import FLAGS
 
 class FieldDumper:
     def __init__(self, path: str, fields, dump_mode: int = 0, dump_interval: int = 10, num_threads: int = 1,
-                 part_bytes: int = 2 << 30, rank: int = 0):
+                 part_bytes: int = 2 << 30, rank: int = 0, user_filename: str = ""):
         """dump_mode 0 = all instances, 1 = hash(lineid) % interval == 0, 2 = every
         ``dump_interval``-th instance."""
         os.makedirs(path, exist_ok=True)
         self.path, self.fields = path, list(fields)
         self.mode, self.interval = dump_mode, max(1, dump_interval)
         self.part_bytes, self.rank = part_bytes, rank
+        self.user_filename = user_filename        # TrainerDesc.user_define_dump_filename: part-<name>-<n>
         self._q: "queue.Queue" = queue.Queue(maxsize=64)
         self._part, self._written, self._fp = 0, 0, None
         self._seen = 0
@@ -33,7 +34,8 @@ class FieldDumper:
     def _open(self):
         if self._fp:
             self._fp.close()
-        self._fp = open(os.path.join(self.path, f"part-{self.rank:03d}-{self._part:05d}"), "w")
+        stem = self.user_filename if self.user_filename else f"{self.rank:03d}"         # (GetDumpPath, ps_gpu_trainer.cc:256-266)
+        self._fp = open(os.path.join(self.path, f"part-{stem}-{self._part:05d}"), "w")
         self._part += 1
         self._written = 0
 

@@ -247,3 +247,49 @@ def test_dump_format_flags_and_record_pool_flags(tmp_path, capsys):
         assert ds._native.idle_records() == 10
     finally:
         set_flags({"enable_force_mem_recyle": False, "padbox_record_pool_max_size": 2000000})
+
+
+def test_trainer_desc_text_and_its_fields(tmp_path):
+    from paddlebox_b200.models.ctr import CtrDnn
+    from paddlebox_b200.ops.pull_box_sparse import SlotBatch
+    from paddlebox_b200.trainer import CTRTrainer, TrainerConfig
+    text = """
+      class_name: "BoxPSTrainer"  device_worker_name: "BoxPSWorker"  thread_num: 8  debug: true
+      dump_fields_path: "%s"  dump_fields: "pred"  dump_fields: "label"  dump_param: "fc_0.w_0"
+      user_define_dump_filename: "join"  enable_random_dump: true  random_with_lineid: true  dump_interval: 3
+      check_nan_var_names: "pred"  loss_names: "loss"  scale_sparse_gradient_with_batch_size: false
+      boxps_param { async_mode: false sync_dense_mode: 1 sync_weight_step: 4 dump_thread_num: 2 param_need_sync: "fc_0.w_0" }
+    """ % str(tmp_path / "dump")
+    cfg = TrainerConfig.from_desc(text)
+    assert cfg.debug and cfg.dump_fields == ["pred", "label"] and cfg.dump_param == ["fc_0.w_0"] and cfg.dump_mode == 1
+    assert cfg.dump_interval == 3 and cfg.user_define_dump_filename == "join" and cfg.check_nan_var_names == ["pred"]
+    assert (cfg.sync_dense_mode, cfg.sync_weight_step, cfg.dump_thread_num) == ("kstep", 4, 2)
+    assert cfg.scale_sparse_gradient_with_batch_size is False and cfg.loss_names == ["loss"]
+    assert TrainerConfig.from_desc('boxps_param { async_mode: true }').sync_dense_mode == "async"
+    assert TrainerConfig.from_desc('debug: false').dump_mode == 0
+
+    def one_step(scale_with_batch):
+        BoxWrapper.reset_instance()
+        box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=0, world_size=1)
+        box.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0, "initial_range": 0.0, "mf_initial_range": 0.01})
+        keys = torch.tensor([3, 4, 5, 6], dtype=torch.int64)
+        batch = SlotBatch(keys, torch.tensor([0, 1, 2, 3, 4], dtype=torch.int32), 2, 2, torch.tensor([[1.0, .5], [0.0, .25]]),
+                          ins_ids=["a x", "b"])
+        box.begin_feed_pass("20240101"); box.feed_pass(keys); box.end_feed_pass(); box.begin_pass()
+        torch.manual_seed(0)
+        c = TrainerConfig(dump_fields=["pred"], dump_fields_path=str(tmp_path / f"d{int(scale_with_batch)}"),
+                          user_define_dump_filename="join", scale_sparse_gradient_with_batch_size=scale_with_batch)
+        tr = CTRTrainer(CtrDnn(num_slots=2, embedx_dim=4, dense_dim=1, hidden=(4,)), box, c)
+        before = box.host_table.fetch_rows(keys.numpy().astype(np.uint64), create=False).copy()
+        tr.train_step(batch)
+        tr.train_step(batch)                                   # (the first push of a key only creates its state)
+        if tr.dumper is not None:
+            tr.dumper.close()
+        box.end_pass()
+        after = box.host_table.fetch_rows(keys.numpy().astype(np.uint64), create=False)
+        BoxWrapper.reset_instance()
+        return np.abs(after[:, 2] - before[:, 2])            # movement of embed_w
+
+    big, small = one_step(True), one_step(False)
+    assert np.all(big > 0) and np.all(small > 0) and np.all(big > small)          # -batch_size vs -1 as the push scale
+    assert os.listdir(tmp_path / "d1") == ["part-join-00000"]
