@@ -185,3 +185,67 @@ def test_batch_dealing_covers_every_instance_once(n_ins, batch, workers):
         seen[starts[i]:starts[i] + lens[i]] += 1
     assert np.all(seen == 1)
     assert n % workers == 0                                  # whole rounds: the same number of batches per worker
+
+
+# ------------------------------------------------------------------------------- protobuf text format
+_names = st.text(alphabet="abcdefghijklmnopqrstuvwxyz_", min_size=1, max_size=8).filter(lambda s: s not in ("true", "false", "inf", "nan"))
+_scalars = st.one_of(st.integers(-10 ** 9, 10 ** 9), st.booleans(),
+                     st.floats(min_value=-1e6, max_value=1e6, allow_nan=False).map(lambda v: round(v, 4)).filter(lambda v: v != int(v)),
+                     st.text(alphabet="abcXYZ012 _-./:{}#", max_size=12))
+
+
+def _messages(depth):
+    if depth == 0:
+        return st.dictionaries(_names, _scalars, max_size=4)
+    return st.dictionaries(_names, st.one_of(_scalars, _messages(depth - 1), st.lists(_scalars, min_size=2, max_size=3)), max_size=4)
+
+
+def _to_text(msg, indent=0):
+    pad = " " * indent
+    out = []
+    for k, v in msg.items():
+        items = v if isinstance(v, list) else [v]
+        for it in items:
+            if isinstance(it, dict):
+                out.append(f"{pad}{k} {{\n{_to_text(it, indent + 2)}{pad}}}\n")
+            elif isinstance(it, bool):
+                out.append(f"{pad}{k}: {'true' if it else 'false'}\n")
+            elif isinstance(it, str):
+                out.append(pad + k + ': "' + it.replace("\\", "\\\\").replace('"', '\\"') + '"\n')
+            else:
+                out.append(f"{pad}{k}: {it!r}\n")
+    return "".join(out)
+
+
+@FAST
+@given(_messages(2))
+def test_protobuf_text_parser_round_trips_nested_messages(msg):
+    from paddlebox_b200.fleet_desc import parse_text_format
+    text = _to_text(msg)
+    got = parse_text_format(text)
+
+    def same(a, b):
+        if isinstance(a, dict):
+            return isinstance(b, dict) and a.keys() == b.keys() and all(same(a[k], b[k]) for k in a)
+        if isinstance(a, list):
+            return isinstance(b, list) and len(a) == len(b) and all(same(x, y) for x, y in zip(a, b))
+        if isinstance(a, float):
+            return abs(a - b) < 1e-9
+        return a == b and type(a) is type(b)
+    assert same(msg, got), (msg, got, text)
+
+
+@FAST
+@given(st.sampled_from([1, 2, 3, 5, 6, 10, 15, 30, 60]), st.integers(1, 6), st.integers(0, 23), st.integers(0, 23), st.booleans())
+def test_online_pass_intervals_cover_the_allowed_hours_in_order(split_interval, per_pass, h0, h1, hourly):
+    from paddlebox_b200.fleet_util import FleetUtil
+    lo, hi = min(h0, h1), max(h0, h1)
+    passes = FleetUtil().get_online_pass_interval("{20240101..20240102}", "{%d..%d}" % (lo, hi), split_interval, per_pass, hourly)
+    flat = [s for p in passes for s in p]
+    assert all(len(p) == per_pass for p in passes)
+    want = []
+    for i in range(24 * 60 // split_interval):
+        h, m = divmod(i * split_interval, 60)
+        if lo <= h <= hi:
+            want.append("%02d" % h if hourly else "%02d%02d" % (h, m))
+    assert flat == want[:len(flat)] and len(want) - len(flat) < per_pass + max(0, len(want) - (24 * 60 // split_interval // per_pass) * per_pass)
