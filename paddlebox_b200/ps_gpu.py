@@ -58,6 +58,7 @@ class PSGPUWrapper(BoxWrapper):
         self._gpu_free.put(None)              # the GPU starts out free
         self.current_task: HeterContext | None = None
         self._running = True
+        self._tasks_queued = 0               # tasks handed to the pre-build thread and not yet taken by begin_pass
         # The pre-build thread exchanges keys between ranks while the main thread trains the previous pass and
         # issues collectives of its own: two threads on one process group would interleave differently on
         # different ranks.  The build thread gets a group of its own (host arrays: gloo), created here, where
@@ -137,15 +138,20 @@ class PSGPUWrapper(BoxWrapper):
         if date:
             self.set_date(date)
         dataset.load_into_memory()
-        task = HeterContext(dataset=dataset, date=date)
+        return self.submit(HeterContext(dataset=dataset, date=date))
+
+    def submit(self, task: HeterContext) -> HeterContext:
+        """Hand a build task to the pre-build thread (``data_ready`` channel); ``begin_pass`` takes the built
+        tasks in this order."""
+        self.start_build_thread()
+        self._tasks_queued += 1
         self._data_ready.put(task)
         return task
 
     def build_task(self, keys=None) -> HeterContext:
         """Queue a build task for an explicit key list (no dataset) and start the pass."""
         self.start_build_thread()
-        task = HeterContext(keys=np.zeros(0, np.uint64) if keys is None else keys)
-        self._data_ready.put(task)
+        task = self.submit(HeterContext(keys=np.zeros(0, np.uint64) if keys is None else keys))
         self.begin_pass()
         return task
 
@@ -155,6 +161,9 @@ class PSGPUWrapper(BoxWrapper):
             return super().begin_pass()
         assert self._initialized, "call init_gpu_ps / initialize_gpu_and_load_model first"
         t0 = time.time()
+        if self._tasks_queued <= 0:
+            raise RuntimeError("begin_pass: no pass is being built (call load_into_memory(dataset) or build_task(keys) first)")
+        self._tasks_queued -= 1
         task = self._buildcpu_ready.get()
         if task.error is not None:
             raise task.error

@@ -600,7 +600,7 @@ def cpu_psgpu_pipeline_two_ranks(rank, world):
         box.start_build_thread()
         from paddlebox_b200.ps_gpu import HeterContext
         task = HeterContext(keys=all_keys[rank] + np.uint64(1000 * p))
-        box._data_ready.put(task)
+        box.submit(task)
         for i in range(25):                                  # "training": collectives on the world group meanwhile
             t = torch.full((64,), float(rank + i))
             dist.all_reduce(t)

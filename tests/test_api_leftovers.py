@@ -293,3 +293,18 @@ def test_trainer_desc_text_and_its_fields(tmp_path):
     big, small = one_step(True), one_step(False)
     assert np.all(big > 0) and np.all(small > 0) and np.all(big > small)          # -batch_size vs -1 as the push scale
     assert os.listdir(tmp_path / "d1") == ["part-join-00000"]
+
+
+def test_psgpu_begin_pass_without_a_queued_task_is_an_error_not_a_hang():
+    from paddlebox_b200.ps_gpu import PSGPUWrapper
+    PSGPUWrapper.reset_instance()
+    try:
+        ps = PSGPUWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=0, world_size=1)
+        ps.init_gpu_ps(conf={})
+        ps.build_task(np.array([1, 2, 3], np.uint64))
+        ps.end_pass()
+        with pytest.raises(RuntimeError):
+            ps.begin_pass()                    # nothing was queued for a second pass
+        ps.finalize()
+    finally:
+        PSGPUWrapper.reset_instance()

@@ -504,8 +504,8 @@ def test_psgpu_pass_pipeline_overlaps_build_with_training(tmp_path):
         ps.init_gpu_ps([0], {"mf_create_thresholds": 0.0})
         ps.start_build_thread()
         t1, t2 = HeterContext(keys=np.arange(1, 101, dtype=np.uint64)), HeterContext(keys=np.arange(50, 301, dtype=np.uint64))
-        ps._data_ready.put(t1)
-        ps._data_ready.put(t2)                            # queued while pass 1 has not even begun
+        ps.submit(t1)
+        ps.submit(t2)                            # queued while pass 1 has not even begun
         ps.begin_pass()
         assert ps.current_task is t1 and np.array_equal(ps._pass_keys, np.arange(0, 101, dtype=np.uint64))
         deadline = time.time() + 10
@@ -525,7 +525,7 @@ def test_psgpu_pass_pipeline_overlaps_build_with_training(tmp_path):
         assert {"pre_build_s", "build_pull_s", "build_gpu_s"} <= set(t2.timing)
         ps.end_pass()
         bad = HeterContext(keys="not keys")
-        ps._data_ready.put(bad)
+        ps.submit(bad)
         with pytest.raises(Exception):
             ps.begin_pass()
         # a dataset through PSGPUTrainer.run
