@@ -738,9 +738,12 @@ class QueueDataset(InMemoryDataset):
             n_cur = cur.num_records()
             self.stream_stats["records"] += n_cur
             loader = _BatchLoader(cur, 0, device, prefetch, with_ins_id, self._want_meta(), getattr(self, "max_rank", 3))
-            yield from (loader.host_batches() if host else iter(loader))
+            try:
+                yield from (loader.host_batches() if host else iter(loader))
+            finally:
+                if th is not None:       # also when the consumer stops early: the next stream reuses the handles
+                    th.join()
             if th is not None:
-                th.join()
                 if err:
                     raise err[0]
                 self.stream_stats["max_resident_records"] = max(self.stream_stats["max_resident_records"],

@@ -708,3 +708,17 @@ def test_run_cmd_and_stage_timers(tmp_path):
     with ct.span("x"):
         pass
     assert ct.summary() == {} or "x" in ct.summary()
+
+
+def test_queue_dataset_stream_can_be_abandoned_and_restarted(tmp_path):
+    import torch
+    from paddlebox_b200.dataset import DatasetFactory
+    from tests.util_data import slot_vars, write_files
+    files = write_files(str(tmp_path), n_files=4, lines_per_file=40, n_sparse=2, n_dense=1, key_space=30)
+    ds = DatasetFactory().create_dataset("QueueDataset")
+    ds.set_use_var(slot_vars(2, 1)); ds.set_batch_size(8); ds.set_thread(1); ds.set_filelist(files)
+    for _ in range(3):
+        it = ds.batches(device=torch.device("cpu"))
+        next(it); next(it)
+        it.close()                              # the consumer walks away in the middle of the first group
+    assert sum(b.batch_size for b in ds.batches(device=torch.device("cpu"))) == 160
