@@ -78,3 +78,81 @@ class Predictor:
 
     def close(self) -> None:
         BoxWrapper.reset_instance()
+
+    # ---- following a training job through its donefiles -------------------------------------------------------
+    def apply_delta(self, xbox_delta: str) -> int:
+        """Bring a newer delta model into the live predictor: rows of the delta replace / extend the loaded ones.
+        On a GPU the device table is rebuilt from the host tier (the working set is the whole serving model)."""
+        n = self.box.load_model(xbox_delta, serving=True)
+        self.rows_loaded += n
+        if self.box.use_cuda:
+            self.box.set_test_mode(False)
+            self.box.end_pass()
+            self.box.begin_feed_pass()
+            self.box.feed_pass(self.box.host_table.keys())
+            self.box.end_feed_pass()
+            self.box.begin_pass()
+            self.box.set_test_mode(True)
+        return n
+
+    @classmethod
+    def from_donefiles(cls, model: torch.nn.Module, output_path: str, **kw) -> "Predictor":
+        """The newest serving model a training job has published under ``output_path`` in the reference's
+        donefile convention (``FleetUtil.write_xbox_donefile`` / ``write_model_donefile``): the last base of
+        ``xbox_base_done.txt``, every delta of ``xbox_patch_done.txt`` written after that base, and the dense
+        parameters next to the last batch model of ``donefile.txt`` (``<day>/<pass>/dense``)."""
+        base, deltas, dense = serving_models_from_donefiles(output_path)
+        p = cls(model, base, deltas, dense_dir=dense, **kw)
+        p._donefile_root, p._applied = output_path, {base, *deltas}
+        return p
+
+    def refresh_from_donefiles(self) -> int:
+        """Apply the deltas published since the last look; returns how many.  (A NEW base means a new day: build a
+        new predictor from it.)"""
+        root = getattr(self, "_donefile_root", None)
+        if root is None:
+            raise RuntimeError("this predictor was not built with from_donefiles")
+        _, deltas, _ = serving_models_from_donefiles(root)
+        fresh = [d for d in deltas if d not in self._applied]
+        for d in fresh:
+            self.apply_delta(d)
+            self._applied.add(d)
+        return len(fresh)
+
+
+def _local_path(input_field: str) -> str:
+    """``hdfs://ns/out/20240102/delta-2/000`` -> ``/out/20240102/delta-2`` (the ``/000`` part suffix and a
+    ``scheme://host`` prefix removed)."""
+    import re
+    p = re.sub(r"^[a-zA-Z][a-zA-Z0-9+.-]*://[^/]*", "", input_field)
+    return p[:-4] if p.endswith("/000") else p
+
+
+def serving_models_from_donefiles(output_path: str):
+    """``(base dir, [delta dirs written after that base, oldest first], dense dir or None)`` from the donefiles
+    of ``output_path`` (formats of ``fleet_util.py``).  A base is written at the END of its day, so the deltas
+    that belong on top of it are those of later days."""
+    import json
+    root = output_path.rstrip("/")
+
+    def lines(name):
+        p = os.path.join(root, name)
+        return [ln for ln in open(p).read().split("\n") if ln.strip()] if os.path.isfile(p) else []
+    bases = [json.loads(ln) for ln in lines("xbox_base_done.txt")]
+    if not bases:
+        raise FileNotFoundError(f"no base model listed in {root}/xbox_base_done.txt")
+    base = _local_path(bases[-1]["input"])
+    base_day = int(base.rstrip("/").split("/")[-2])
+    deltas = []
+    for ln in lines("xbox_patch_done.txt"):
+        d = _local_path(json.loads(ln)["input"])
+        if int(d.rstrip("/").split("/")[-2]) > base_day:
+            deltas.append(d)
+    dense = None
+    rows = [ln.split("\t") for ln in lines("donefile.txt")]
+    for r in reversed(rows):
+        cand = os.path.join(r[2], "dense") if len(r) > 2 else ""
+        if cand and os.path.isdir(cand):
+            dense = cand
+            break
+    return base, deltas, dense

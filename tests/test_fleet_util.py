@@ -333,3 +333,70 @@ def test_role_makers_join_the_world_from_the_paddle_launcher_environment(kind, t
         assert o["eps"] == eps.split(",")
     if kind == "general":
         assert outs[2] == {"server": 0}
+
+
+def test_predictor_follows_a_job_through_its_donefiles(tmp_path):
+    """Serving side of the loop: the online example trains two days; a predictor built from the donefiles loads
+    the last base; a further day's deltas are picked up by ``refresh_from_donefiles``."""
+    import subprocess
+    import sys
+    from paddlebox_b200.models.ctr import build_model
+    from paddlebox_b200.ops.pull_box_sparse import SlotBatch
+    from paddlebox_b200.serving import Predictor, serving_models_from_donefiles
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = {k: v for k, v in os.environ.items() if k not in ("RANK", "WORLD_SIZE", "LOCAL_RANK")}
+    out = str(tmp_path / "job")
+    cmd = [sys.executable, os.path.join(root, "examples", "online_train.py"), "--cpu", "--out", out, "--lines", "128"]
+    assert subprocess.run(cmd + ["--days", "20240101,20240102"], capture_output=True, text=True, env=env, timeout=600).returncode == 0
+    base, deltas, dense = serving_models_from_donefiles(out)
+    assert base == f"{out}/20240102/base" and deltas == [] and dense == f"{out}/20240102/0/dense"
+    BoxWrapper.reset_instance()
+    model = build_model("deepfm", num_slots=6, embedx_dim=8, dense_dim=3, hidden=(64, 32))
+    p = Predictor.from_donefiles(model, out, embedx_dim=8, device=torch.device("cpu"))
+    try:
+        n0 = p.num_features
+        assert n0 > 100 and p.refresh_from_donefiles() == 0
+        keys = torch.tensor(p.box.host_table.keys()[:12].astype(np.int64))
+        batch = SlotBatch(keys, torch.arange(0, 13, dtype=torch.int32), 2, 6, torch.rand(2, 4))
+        before = p.predict(batch).clone()
+        assert before.shape == (2,) and torch.all((before > 0) & (before < 1))
+        # the job trains one more day: two new deltas appear in xbox_patch_done.txt (and a new base at its end)
+        assert subprocess.run(cmd + ["--days", "20240101,20240102,20240103"], capture_output=True, text=True, env=env,
+                              timeout=600).returncode == 0
+        # (serving_models_from_donefiles now names the new base; the live predictor follows the deltas of its own base)
+        p._donefile_root = out
+        lines = [ln for ln in open(f"{out}/xbox_patch_done.txt").read().split("\n") if ln.strip()]
+        assert len(lines) == 6
+        import json as _json
+        new_deltas = [os.path.dirname(_json.loads(ln)["input"]) for ln in lines[-2:]]
+        got = sum(p.apply_delta(d) > 0 for d in new_deltas)
+        assert got == 2 and p.num_features >= n0
+        after = p.predict(batch)
+        assert not torch.equal(before, after)                    # the rows moved with the new day's training
+    finally:
+        p.close()
+
+
+def test_predictor_refresh_picks_up_new_deltas(tmp_path, box):
+    from paddlebox_b200.models.ctr import CtrDnn
+    from paddlebox_b200.serving import Predictor
+    out = str(tmp_path / "o")
+    u = FU.FleetUtil(box=box)
+    _touch(box, range(1, 41))
+    u.save_xbox_base_model(out, 20240101); u.write_xbox_donefile(out, 20240101, -1, 7, "/d")
+    _touch(box, range(30, 61))
+    u.save_delta_model(out, 20240102, 1); u.write_xbox_donefile(out, 20240102, 1, 7, "/d")
+    BoxWrapper.reset_instance()
+    p = Predictor.from_donefiles(CtrDnn(num_slots=2, embedx_dim=4, dense_dim=1, hidden=(4,)), out, embedx_dim=4,
+                                 device=torch.device("cpu"))
+    try:
+        assert p.num_features == 61 and p.refresh_from_donefiles() == 0        # 60 keys + the always-present key 0
+        # the training job (another process in real life) publishes the next delta
+        b2 = BoxWrapper(embedx_dim=4, device=torch.device("cpu"), rank=0, world_size=1)
+        b2.initialize_gpu_and_load_model({"mf_create_thresholds": 0.0})
+        u2 = FU.FleetUtil(box=b2)
+        _touch(b2, range(55, 81))
+        u2.save_delta_model(out, 20240102, 2); u2.write_xbox_donefile(out, 20240102, 2, 7, "/d")
+        assert p.refresh_from_donefiles() == 1 and p.num_features == 81 and p.refresh_from_donefiles() == 0
+    finally:
+        p.close()
