@@ -480,6 +480,12 @@ class BoxWrapper:
         the data-parallel group and resets the metric (box_wrapper.cc:1027-1046)."""
         return self._metrics[name].get_metric_msg(self._metric_group())
 
+    def get_wuauc_metric_msg(self, name: str) -> list:
+        """``[user_cnt, size, sum of user AUCs, sum of (user AUC * instances), uauc, wuauc]`` over all ranks
+        (``GetWuAucMetricMsg``, metrics.h:774-805); resets the metric."""
+        uauc, wuauc, users, size = self._metrics[name].get_metric_msg(self._metric_group())
+        return [users, size, uauc * users, wuauc * size, uauc, wuauc]
+
     def get_continue_metric_msg(self, name: str) -> list:
         """[mae, rmse, actual value, predicted value, size] of a continuous-value metric
         (``GetContinueMetricMsg``, box_wrapper.cc:1048-1065); resets it."""

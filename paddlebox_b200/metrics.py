@@ -261,10 +261,21 @@ class WuAucMetricMsg(MetricMsg):
             self.calc.add_uid(p, y, u)
 
     def get_metric_msg(self, group=None):
+        """``[uauc, wuauc, user_cnt, size]``.  Over several ranks the per-user AUCs are computed where the
+        records are (a user seen on two ranks counts as two users there, as in the reference) and the SUMS are
+        reduced: uauc = sum(auc) / users, wuauc = sum(auc * ins) / size (``GetWuAucMetricMsg``, metrics.h:774-805)."""
         self._flush_uid()
-        out = self.calc.compute_wuauc()   # [uauc, wuauc, user_cnt, size]
+        uauc, wuauc, users, size = self.calc.compute_wuauc()
         self.calc.reset()
-        return out
+        if group is not None:
+            import torch.distributed as dist
+            t = torch.tensor([users, size, uauc * users, wuauc * size], dtype=torch.float64)
+            if dist.get_backend(group) == "nccl":
+                t = t.cuda()
+            dist.all_reduce(t, group=group)
+            users, size, su, sw = t.tolist()
+            uauc, wuauc = su / (users + 1e-10), sw / (size + 1e-10)
+        return [uauc, wuauc, users, size]
 
 
 class NanInfMetricMsg(MetricMsg):

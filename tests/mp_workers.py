@@ -733,3 +733,27 @@ def cpu_preload_overlap_two_ranks(rank, world, data_dir):
     assert all(torch.allclose(g[0], t) for t in g)
     BoxWrapper.reset_instance()
     return {"sizes": sizes, "steps": steps, "keys_total": int(tot)}
+
+
+def cpu_wuauc_two_ranks(rank, world):
+    """Per-user AUC over two ranks: users live on one rank each here, so the reduced result must equal the
+    single-process result on the union of the records."""
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    from paddlebox_b200.metrics import create_metric
+    g = torch.Generator().manual_seed(5)
+    n = 4000
+    uid = torch.randint(0, 60, (n,), generator=g)
+    pred = torch.rand(n, generator=g)
+    label = (torch.rand(n, generator=g) < pred).float()
+    whole = create_metric("WuAucCalculator", name="w", uid_varname="uid")
+    whole.add_data({"pred": pred, "label": label, "uid": uid})
+    want = whole.get_metric_msg()
+    box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"), rank=rank, world_size=world)
+    box.initialize_gpu_and_load_model({})
+    box.init_metric("WuAucCalculator", "w", uid_varname="uid", metric_phase=1)
+    mine = (uid % world) == rank
+    box.get_metric("w").add_data({"pred": pred[mine], "label": label[mine], "uid": uid[mine]})
+    got = box.get_wuauc_metric_msg("w")
+    BoxWrapper.reset_instance()
+    assert abs(got[4] - want[0]) < 1e-9 and abs(got[5] - want[1]) < 1e-9 and got[0] == want[2] and got[1] == want[3], (got, want)
+    return got

@@ -149,6 +149,11 @@ def test_next_pass_is_fed_while_the_current_one_trains_two_ranks(tmp_path):
     assert outs[0]["sizes"] == [4 * 48, 4 * 64, 4 * 48] and outs[0]["keys_total"] > 150
 
 
+def test_per_user_auc_is_reduced_over_ranks():
+    outs = _spawn(W.cpu_wuauc_two_ranks, 2, "gloo")
+    assert outs[0] == outs[1] and outs[0][0] == 60 and outs[0][1] == 4000
+
+
 def test_legacy_record_global_shuffle_two_ranks_gloo():
     outs = _spawn(W.cpu_legacy_global_shuffle, 2, "gloo")
     assert outs[0]["total_before"] == outs[0]["total_after"] == 110 and all(o["owner_ok"] for o in outs)
