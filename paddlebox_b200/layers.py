@@ -20,6 +20,11 @@ from .ops.pull_box_sparse import (SlotBatch, pull_box_extended_sparse, pull_box_
                                   split_by_slot)
 from .ops.seqpool import (SeqpoolAttrs, fused_seqpool_cvm, fused_seqpool_cvm_tradew, fused_seqpool_cvm_with_conv,  # noqa: F401
                           fused_seqpool_cvm_with_credit, fused_seqpool_cvm_with_diff_thres, split_slots)
+from .ops.sequence import (bpr_loss, hash, log_loss, margin_rank_loss, match_matrix_tensor, rank_loss,  # noqa: F401
+                           sequence_concat, sequence_conv, sequence_enumerate, sequence_expand, sequence_expand_as,
+                           sequence_first_step, sequence_last_step, sequence_mask, sequence_pad, sequence_pool,
+                           sequence_reshape, sequence_reverse, sequence_scatter, sequence_slice, sequence_softmax,
+                           sequence_topk_avg_pooling, sequence_unpad, teacher_student_sigmoid_loss)
 from .ops.tdm import TDMTree, tdm_child, tdm_sampler  # noqa: F401
 from .ps_gpu import pull_gpups_sparse  # noqa: F401
 

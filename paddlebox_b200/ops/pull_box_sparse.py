@@ -59,6 +59,13 @@ class SlotBatch:
             out[:n] = torch.bucketize(torch.arange(n), ends, right=True).int()
         return out[:n]
 
+    def slot_lod(self, slot: int) -> torch.Tensor:
+        """int64 [B + 1] offsets of one slot's bags inside that slot's rows (``split_by_slot(emb, batch)[slot]``):
+        the ``lod`` the ragged ops of ``ops/sequence.py`` take."""
+        B = self.batch_size
+        seg = self.lod[slot * B:(slot + 1) * B + 1].long()
+        return seg - seg[0]
+
     def slot_ranges(self):
         """[(begin, end)] of every slot's rows in the slot-major key order (host sync)."""
         b = self.lod[::self.batch_size].tolist()
