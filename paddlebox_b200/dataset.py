@@ -206,6 +206,9 @@ class DatasetBase:
         """pybind name of ``set_thread`` (data_set_py.cc)."""
         self.set_thread(thread_num)
 
+    def _desc(self) -> str:
+        return self.desc()
+
     def set_data_feed_desc(self, desc: str):
         """Configure from the protobuf TEXT form of a ``DataFeedDesc`` (data_feed.proto:18-57; what ``desc()``
         prints and what the reference hands its native dataset): name, batch size, pipe command, threads, slots
@@ -244,6 +247,26 @@ class DatasetBase:
                             ("sample_rate", "set_sample_rate"), ("graph_config", "set_graph_config")):
             if key in d and hasattr(self, setter):
                 getattr(self, setter)(d[key])
+
+    def _check_use_var_with_data_generator(self, var_list, data_generator_class, test_file: str) -> None:
+        """Run the job's data generator over ``test_file`` and check every sample against ``var_list``: same
+        number of slots, no empty slot, float slots hold floats and id slots ints (fleet dataset.py:275-335)."""
+        n = len(var_list)
+        with open(test_file) as f:
+            for line in f:
+                for sample in data_generator_class.generate_sample(line)():
+                    if len(sample) != n:
+                        raise ValueError(f"var length mismatch error: var_list = {n} vs data_generator = {len(sample)}")
+                    for var, (name, vals) in zip(var_list, sample):
+                        if len(vals) == 0:
+                            raise ValueError(f"var length error: var {name}'s length in data_generator is 0")
+                        is_float = str(getattr(var, "dtype", "")).lower().replace("torch.", "") in ("float32", "float", "fp32")
+                        if is_float and not all(isinstance(e, float) for e in vals):
+                            raise TypeError(f"var dtype mismatch error: var name = {name}, var type in var_list = float, "
+                                            f"while var in data_generator contains non-float value, which is {vals}")
+                        if not is_float and not all(isinstance(e, int) for e in vals):
+                            raise TypeError(f"var dtype mismatch error: var name = {name}, var type in var_list = int, "
+                                            f"while var in data_generator contains non-int value, which is {vals}")
 
     def desc(self) -> str:
         """Protobuf text of the feed configuration (``DataFeedDesc``, data_feed.proto:45-57); round-trips through
@@ -573,6 +596,13 @@ class InMemoryDataset(DatasetBase):
 
     def unique_keys(self) -> np.ndarray:
         return self._native.unique_keys()
+
+    def _generate_local_tables_unlock(self, table_id=0, fea_dim=0, read_thread_num=1, consume_thread_num=1,
+                                      shard_num=1) -> int:
+        """The reference builds per-shard key tables from the loaded records for the heterogeneous PS
+        (fleet dataset.py:783-787, data_set.cc ``GenerateLocalTablesUnlock``).  Here the reader threads collect
+        the keys while loading; this returns how many distinct keys the loaded data holds."""
+        return int(self.unique_keys().size)
 
     def stats(self) -> str:
         return self._native.stats()

@@ -134,6 +134,8 @@ class _Util:
 
 util = _Util()
 
+from . import fleet_metrics as metrics  # noqa: E402,F401  ``fleet.metrics.auc(stat_pos, stat_neg)`` ...
+
 
 # ---- the parameter-server calls of the reference's pslib fleet ------------------------------------------------
 # (python/paddle/fluid/incubate/fleet/parameter_server/pslib/__init__.py:214-800).  Job scripts written for the
@@ -281,7 +283,9 @@ def distributed_optimizer(optimizer, strategy=None):
             box.host_table.set_config(cfg)
             if getattr(box, "table", None) is not None:
                 box.table.set_config(cfg)
-    return optimizer if isinstance(optimizer, BoxPSOptimizer) else BoxPSOptimizer(optimizer)
+    global _last_optimizer
+    _last_optimizer = optimizer if isinstance(optimizer, BoxPSOptimizer) else BoxPSOptimizer(optimizer)
+    return _last_optimizer
 
 
 # ---- the remaining role / topology queries of fleet_base.py -------------------------------------------------
@@ -373,3 +377,110 @@ def _get_heter_file_shard(self, files):
 
 
 _Util.get_heter_file_shard = _get_heter_file_shard
+
+
+# ---- the rest of the pslib / fleet-base surface ---------------------------------------------------------------
+_whitelist: np.ndarray | None = None
+_client_config: dict = {}
+_last_optimizer = None
+
+
+def split_files(files) -> list:
+    """This worker's block of ``files`` (fleet_base.py:154-191): as ``util.get_file_shard``; a list is required."""
+    if not isinstance(files, list):
+        raise TypeError("files should be a list of file need to be read.")
+    return util.get_file_shard(files)
+
+
+def all_reduce_worker(input, output) -> None:
+    """``output[:] = sum over workers of input`` (role-maker collective, fleet_base.py:203-213)."""
+    np.asarray(output)[...] = util.all_reduce(np.asarray(input), "sum")
+
+
+def is_xpu() -> bool:
+    return False
+
+
+def set_pull_local_thread_num(thread_num: int) -> None:
+    """Threads of the host side of a sparse pull (pslib :231-235): here the threads that fetch host-table rows into
+    the staging slots when a pass is built (``FLAGS.pbx_pass_fetch_threads``; takes effect at the next wrapper)."""
+    _client_config["pull_local_thread_num"] = int(thread_num)
+    from .flags import FLAGS
+    FLAGS.pbx_pass_fetch_threads = max(1, int(thread_num))
+
+
+def _set_client_communication_config(request_timeout_ms: int, connect_timeout_ms: int, max_retry: int) -> None:
+    """Kept for scripts that tune the PS client (pslib :221-229); there is no RPC client here, the values are stored."""
+    _client_config.update(request_timeout_ms=request_timeout_ms, connect_timeout_ms=connect_timeout_ms, max_retry=max_retry)
+
+
+def confirm() -> None:
+    """``confirm`` / ``revert`` bracket a save on the reference's servers (pslib :520-548: keep or undo the delta
+    flags of the last save).  Saves here move the delta baseline only after every part file is written, so there
+    is nothing to undo; both are barriers."""
+    barrier_worker()
+
+
+def revert() -> None:
+    barrier_worker()
+
+
+def load_pslib_whitelist(table_id, model_path: str, **kwargs) -> int:
+    """Read a key whitelist (one unsigned key per line, first column) for ``save_model_with_whitelist``
+    (pslib :424-441).  ``model_path`` is a file or a directory of ``part-*`` files."""
+    global _whitelist
+    paths = [os.path.join(model_path, n) for n in sorted(os.listdir(model_path))] if os.path.isdir(model_path) else [model_path]
+    keys = []
+    for p in paths:
+        with open(p) as f:
+            keys += [int(ln.split()[0]) for ln in f if ln.strip()]
+    _whitelist = np.unique(np.asarray(keys, dtype=np.uint64))
+    return int(_whitelist.size)
+
+
+def save_model_with_whitelist(executor=None, dirname: str = "", whitelist_path: str = "", main_program=None, **kwargs) -> int:
+    """``save_persistables`` restricted to the keys of a whitelist (pslib :372-422); returns the rows written here."""
+    from .host import HostTable
+    if whitelist_path:
+        load_pslib_whitelist(kwargs.get("table_id", 0), whitelist_path)
+    if _whitelist is None:
+        raise ValueError("save_model_with_whitelist: no whitelist (pass whitelist_path or call load_pslib_whitelist)")
+    mode = int(kwargs.get("mode", 0))
+    box = _box()
+    box._sync_to_host()
+    src = box.host_table
+    present = np.intersect1d(src.keys(), _whitelist)
+    part = HostTable(src.embedx_dim, src.optimizer, src.config)
+    if present.size:
+        part.store_rows(present, src.fetch_rows(present, create=False))
+    n = part.save(dirname, mode=0 if mode == 3 else mode, shard_base=box.rank, clear_dirty=False)
+    barrier_worker()
+    return n
+
+
+def train_from_dataset(model, dataset, trainer=None, **kwargs) -> dict:
+    """``fleet.train_from_dataset`` (pslib :236-247): one pass of ``dataset`` through the job's trainer."""
+    from .trainer import Executor
+    if trainer is not None:
+        return trainer.train_from_dataset(dataset)
+    return Executor().train_from_dataset(model, dataset, **kwargs)
+
+
+def _opt():
+    if _last_optimizer is None:
+        raise RuntimeError("call fleet.distributed_optimizer(...) first")
+    return _last_optimizer
+
+
+def minimize(model, startup_program=None, parameter_list=None, no_grad_set=None):
+    """``fleet.minimize(loss)`` of fleet 2.0 (fleet_base.py:1400-1460) on the optimizer ``distributed_optimizer``
+    returned: builds the job's trainer for ``model``."""
+    return _opt().minimize(model, startup_program, parameter_list, no_grad_set)
+
+
+def get_dist_env() -> dict:
+    """Rank / world size / endpoints of this trainer (pslib :1190-1218)."""
+    eps = worker_endpoints()
+    r = worker_index()
+    return {"trainer_id": r, "num_trainers": worker_num(), "current_endpoint": eps[r] if r < len(eps) else "",
+            "trainer_endpoints": eps}

@@ -234,3 +234,34 @@ def sparse_config_from_strategy(strategy: dict, prefix: str = ""):
               "show_click_decay_rate": float(g("sparse_show_click_decay_rate", 0.98)),
               "delete_threshold": float(g("sparse_delete_threshold", 0.8))}
     return conf, optimizer, {"embedx_dim": int(g("sparse_embedx_dim", 8))}, policy
+
+
+def format_text(msg: dict, indent: int = 0, enums: tuple = ()) -> str:
+    """Nested dicts -> protobuf text (the inverse of ``parse_text_format``): a list is a repeated field, a dict a
+    sub-message, a bool ``true`` / ``false``, a str a quoted string unless its field name is listed in ``enums``."""
+    pad = "  " * indent
+    out = []
+
+    def one(key, v):
+        if isinstance(v, dict):
+            out.append(f"{pad}{key} {{")
+            body = format_text(v, indent + 1, enums)
+            if body:
+                out.append(body)
+            out.append(f"{pad}}}")
+        elif isinstance(v, bool):
+            out.append(f"{pad}{key}: {'true' if v else 'false'}")
+        elif isinstance(v, str):
+            if key in enums:
+                out.append(f"{pad}{key}: {v}")
+            else:
+                out.append(pad + key + ': "' + v.replace("\\", "\\\\").replace('"', '\\"').replace("\n", "\\n") + '"')
+        else:
+            out.append(f"{pad}{key}: {v}")
+
+    for key, val in msg.items():
+        if val is None:
+            continue
+        for v in (val if isinstance(val, (list, tuple)) else [val]):
+            one(key, v)
+    return "\n".join(out)

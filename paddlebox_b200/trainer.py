@@ -506,6 +506,18 @@ class Executor:
         t = self._trainers.get(id(program))
         if t is None:
             cfg = kw.pop("config", None) or getattr(program, "_pipeline_opt", None)
+            fleet_opt = getattr(program, "_fleet_opt", None)
+            if isinstance(cfg, dict) or (cfg is None and isinstance(fleet_opt, dict)):
+                # the reference's path: program._fleet_opt / _pipeline_opt dict -> TrainerFactory -> TrainerDesc
+                # (executor.py _prepare_trainer); the description is turned into this trainer's config
+                from .trainer_desc import TrainerFactory
+                info = dict(fleet_opt or {})
+                info.setdefault("trainer", "BoxPSTrainer" if isinstance(cfg, dict) else "MultiTrainer")
+                info.setdefault("device_worker", "BoxPSWorker" if isinstance(cfg, dict) else "Hogwild")
+                desc = TrainerFactory()._create_trainer(info)
+                desc._set_program(program)
+                desc._gen_trainer_desc()
+                cfg = desc.to_config()
             t = self._trainers[id(program)] = CTRTrainer(program, config=cfg)
         return t
 

@@ -254,6 +254,9 @@ def cpu_global_shuffle_and_cluster(rank, world):
     assert shard == ([f"f{i}" for i in range(3)] if rank == 0 else ["f3", "f4"])
     assert fleet.util.all_reduce(rank + 1, "max") == world and fleet.util.all_gather(rank) == list(range(world))
     c.barrier()
+    if rank == 0:
+        import shutil
+        shutil.rmtree(base, ignore_errors=True)
     return dict(before=n_before, after=n_after, total_before=total_before, total_after=total_after,
                 biggest=biggest, sums=sums.tolist(), ranks=ranks)
 
@@ -756,4 +759,32 @@ def cpu_wuauc_two_ranks(rank, world):
     got = box.get_wuauc_metric_msg("w")
     BoxWrapper.reset_instance()
     assert abs(got[4] - want[0]) < 1e-9 and abs(got[5] - want[1]) < 1e-9 and got[0] == want[2] and got[1] == want[3], (got, want)
+    return got
+
+
+def cpu_fleet_metrics_two_ranks(rank, world):
+    """fleet.metrics over two workers = the single-process value on the union of the statistics."""
+    from paddlebox_b200 import fleet
+    g = torch.Generator().manual_seed(11)
+    n, buckets = 3000, 256
+    pred = torch.rand(n, generator=g)
+    label = (torch.rand(n, generator=g) < pred).long()
+    mine = (torch.arange(n) % world) == rank
+
+    def stats(p, l):
+        b = (p * buckets).long().clamp(max=buckets - 1)
+        return (torch.bincount(b[l == 1], minlength=buckets).view(1, -1), torch.bincount(b[l == 0], minlength=buckets).view(1, -1))
+
+    class _Solo:
+        def all_reduce(self, v, mode="sum"):
+            return v
+    want = fleet.metrics.auc(*stats(pred, label), util=_Solo())
+    got = fleet.metrics.auc(*stats(pred[mine], label[mine]))
+    err = (pred - label).abs()
+    mae = fleet.metrics.mae(err[mine].sum().view(1), torch.tensor([float(mine.sum())]))
+    rmse = fleet.metrics.rmse((err[mine] ** 2).sum().view(1), [float(mine.sum())])
+    assert abs(got - want) < 1e-12 and abs(mae - float(err.mean())) < 1e-6 and abs(rmse - float((err ** 2).mean().sqrt())) < 1e-6
+    assert fleet.metrics.sum([rank + 1.0]).tolist() == [3.0] and fleet.metrics.max([rank]).tolist() == [1.0]
+    assert fleet.metrics.min(np.array([rank, 5])).tolist() == [0.0, 5.0]
+    assert abs(fleet.metrics.acc([3.0 * (rank + 1)], [10.0]) - 9.0 / 20.0) < 1e-12
     return got

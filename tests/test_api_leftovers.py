@@ -308,3 +308,32 @@ def test_psgpu_begin_pass_without_a_queued_task_is_an_error_not_a_hang():
         ps.finalize()
     finally:
         PSGPUWrapper.reset_instance()
+
+
+def test_dataset_generator_check_and_local_tables(tmp_path):
+    from paddlebox_b200.data_generator import MultiSlotDataGenerator
+    from paddlebox_b200.dataset import DatasetFactory, dense_slot, sparse_slot
+
+    class Gen(MultiSlotDataGenerator):
+        def generate_sample(self, line):
+            def it():
+                a, b = line.split()
+                yield [("ids", [int(a)]), ("score", [float(b)])]
+            return it
+
+    class BadGen(Gen):
+        def generate_sample(self, line):
+            def it():
+                yield [("ids", [1]), ("score", [2])]               # an int in a float slot
+            return it
+    f = tmp_path / "part"
+    f.write_text("3 0.5\n4 1.5\n")
+    ds = DatasetFactory().create_dataset("InMemoryDataset")
+    use = [sparse_slot("ids"), dense_slot("score", 1)]
+    ds._check_use_var_with_data_generator(use, Gen(), str(f))
+    with pytest.raises(TypeError):
+        ds._check_use_var_with_data_generator(use, BadGen(), str(f))
+    with pytest.raises(ValueError):
+        ds._check_use_var_with_data_generator(use[:1], Gen(), str(f))
+    ds.set_use_var(use)
+    assert ds._desc() == ds.desc()

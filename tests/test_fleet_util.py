@@ -400,3 +400,48 @@ def test_predictor_refresh_picks_up_new_deltas(tmp_path, box):
         assert p.refresh_from_donefiles() == 1 and p.num_features == 81 and p.refresh_from_donefiles() == 0
     finally:
         p.close()
+
+
+def test_fleet_whitelist_save_split_files_and_small_calls(tmp_path):
+    import numpy as np
+    from paddlebox_b200 import fleet
+    from paddlebox_b200.flags import FLAGS
+    from paddlebox_b200.host import HostTable
+    box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"))
+    box.initialize_gpu_and_load_model({})
+    keys = np.arange(1, 41, dtype=np.uint64)
+    rows = box.host_table.fetch_rows(keys, create=True)
+    rows[:, 0] = 5.0
+    box.host_table.store_rows(keys, rows)
+    wl = tmp_path / "white.txt"
+    wl.write_text("".join(f"{k}\t1\n" for k in (3, 7, 11, 1000)))
+    assert fleet.load_pslib_whitelist(0, str(wl)) == 4
+    n = fleet.save_model_with_whitelist(None, str(tmp_path / "wl_model"), mode=0)
+    assert n == 3                                                          # key 1000 is not in the table
+    back = HostTable(box.host_table.embedx_dim, box.host_table.optimizer, box.host_table.config)
+    assert back.load(str(tmp_path / "wl_model")) == 3 and sorted(back.keys().tolist()) == [3, 7, 11]
+    np.testing.assert_allclose(back.fetch_rows(np.array([7], np.uint64), create=False), rows[6:7])
+    assert fleet.save_model_with_whitelist(None, str(tmp_path / "wl2"), str(wl), mode=0) == 3
+    assert box.host_table.size() == 40                                     # the table itself is untouched
+
+    assert fleet.split_files(["a", "b", "c"]) == ["a", "b", "c"]
+    with pytest.raises(TypeError):
+        fleet.split_files("a,b")
+    out = np.zeros(2)
+    fleet.all_reduce_worker(np.array([1.0, 2.0]), out)
+    assert out.tolist() == [1.0, 2.0] and fleet.is_xpu() is False
+    old = FLAGS.pbx_pass_fetch_threads
+    fleet.set_pull_local_thread_num(3)
+    assert FLAGS.pbx_pass_fetch_threads == 3
+    FLAGS.pbx_pass_fetch_threads = old
+    fleet._set_client_communication_config(1000, 2000, 3)
+    fleet.confirm()
+    fleet.revert()
+    env = fleet.get_dist_env()
+    assert env["trainer_id"] == 0 and env["num_trainers"] == 1
+    opt = fleet.distributed_optimizer(__import__("paddlebox_b200.optimizer", fromlist=["x"]).DenseOptimizerSpec("adam", 1e-3))
+    m = torch.nn.Linear(2, 1)
+    cfg = fleet.minimize(m)
+    assert m._pipeline_opt is cfg and opt is fleet._last_optimizer
+    assert abs(fleet.metrics.mae([2.0], [4.0]) - 0.5) < 1e-12
+    BoxWrapper.reset_instance()

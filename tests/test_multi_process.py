@@ -149,6 +149,11 @@ def test_next_pass_is_fed_while_the_current_one_trains_two_ranks(tmp_path):
     assert outs[0]["sizes"] == [4 * 48, 4 * 64, 4 * 48] and outs[0]["keys_total"] > 150
 
 
+def test_fleet_metrics_reduce_statistics_over_workers():
+    outs = _spawn(W.cpu_fleet_metrics_two_ranks, 2, "gloo")
+    assert outs[0] == outs[1] and 0.5 < outs[0] < 1.0
+
+
 def test_per_user_auc_is_reduced_over_ranks():
     outs = _spawn(W.cpu_wuauc_two_ranks, 2, "gloo")
     assert outs[0] == outs[1] and outs[0][0] == 60 and outs[0][1] == 4000

@@ -233,6 +233,9 @@ def test_protobuf_text_parser_round_trips_nested_messages(msg):
             return abs(a - b) < 1e-9
         return a == b and type(a) is type(b)
     assert same(msg, got), (msg, got, text)
+    from paddlebox_b200.fleet_desc import format_text
+    again = parse_text_format(format_text(msg))                   # the framework's own writer reads back the same
+    assert same(msg, again), (msg, again, format_text(msg))
 
 
 @FAST
