@@ -12,7 +12,7 @@ cd "$(dirname "$0")/.."
 OUT=${1:-profiles}
 mkdir -p "$OUT"
 shift || true
-ARGS=${*:-tests/test_host_runtime.py tests/test_api_sweep.py tests/test_cpu_e2e.py tests/test_graph.py tests/test_legacy_feed.py tests/test_pass_build.py tests/test_properties.py}
+ARGS=${*:-tests/test_host_runtime.py tests/test_api_sweep.py tests/test_cpu_e2e.py tests/test_graph.py tests/test_legacy_feed.py tests/test_pass_build.py tests/test_properties.py tests/test_index_dataset.py}
 TMP=$(mktemp -d)
 SAN=${SAN:-asan}
 if [ $SAN = tsan ]; then

@@ -224,6 +224,12 @@ int pbh_dataset_slots_shuffle(void* h, const int* slots, int n, uint64_t seed) {
 int pbh_dataset_slots_shuffle_back(void* h, const int* slots, int n, uint64_t seed) {
   return ((Dataset*)h)->slots_shuffle(std::vector<int>(slots, slots + n), seed, true);
 }
+int pbh_dataset_slot_first_values(void* h, int slot, uint64_t* out, uint8_t* has) {
+  return ((Dataset*)h)->slot_first_values(slot, out, has);
+}
+int pbh_dataset_expand_records(void* h, int slot, int label_slot, const int64_t* counts, const uint64_t* ids, const uint8_t* neg) {
+  return ((Dataset*)h)->expand_records(slot, label_slot, counts, ids, neg);
+}
 int pbh_dataset_prepare_train(void* h, int nworkers, int shuffle, uint64_t seed, int64_t min_batches) {
   return ((Dataset*)h)->prepare_train(nworkers, shuffle != 0, seed, min_batches);
 }

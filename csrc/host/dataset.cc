@@ -758,6 +758,65 @@ int Dataset::slots_shuffle(const std::vector<int>& slot_idx, uint64_t seed, bool
   return 0;
 }
 
+int Dataset::slot_first_values(int slot, uint64_t* out, uint8_t* has) const {
+  PBH_REQUIRE(!arena_only_, "slot_first_values needs records: not available for a pass loaded from a pass file");
+  PBH_REQUIRE(slot >= 0 && slot < (int)slots.size() && slot_to_sparse_[slot] >= 0, "slot %d is not a used sparse slot", slot);
+  const int p = slot_to_sparse_[slot];
+  for (size_t i = 0; i < records_.size(); ++i) {
+    const SlotRecord* r = records_[i];
+    const bool ok = p + 1 < (int)r->u64_offs.size() && r->u64_offs[p + 1] > r->u64_offs[p];
+    has[i] = ok ? 1 : 0;
+    out[i] = ok ? r->u64_vals[r->u64_offs[p]] : 0;
+  }
+  return 0;
+}
+
+int Dataset::expand_records(int slot, int label_slot, const int64_t* counts, const uint64_t* ids, const uint8_t* neg) {
+  PBH_REQUIRE(!arena_only_, "expand_records needs records: not available for a pass loaded from a pass file");
+  PBH_REQUIRE(slot >= 0 && slot < (int)slots.size() && slot_to_sparse_[slot] >= 0, "slot %d is not a used sparse slot", slot);
+  int lp = -1, lf = -1;
+  if (label_slot >= 0) {
+    PBH_REQUIRE(label_slot < (int)slots.size(), "label slot %d out of range", label_slot);
+    lp = slot_to_sparse_[label_slot];
+    lf = lp < 0 ? float_idx_[label_slot] : -1;
+    PBH_REQUIRE(lp >= 0 || lf >= 0, "label slot %d is not a used slot", label_slot);
+  }
+  drop_arena();
+  const int p = slot_to_sparse_[slot];
+  std::vector<SlotRecord*> out, dropped;
+  int64_t k = 0, total = 0;
+  for (size_t i = 0; i < records_.size(); ++i) {
+    PBH_REQUIRE(counts[i] >= 0, "negative copy count for record %zu", i);
+    total += counts[i];
+  }
+  out.reserve((size_t)total);
+  for (size_t i = 0; i < records_.size(); ++i) {
+    SlotRecord* r = records_[i];
+    const bool has = p + 1 < (int)r->u64_offs.size() && r->u64_offs[p + 1] > r->u64_offs[p];
+    if (counts[i] == 0 || !has) { dropped.push_back(r); k += counts[i]; continue; }
+    for (int64_t c = 0; c < counts[i]; ++c, ++k) {
+      SlotRecord* n = (c + 1 == counts[i]) ? r : new SlotRecord(*r);   // the original is the last copy
+      n->u64_vals[n->u64_offs[p]] = ids[k];
+      if (neg[k]) {
+        if (lp >= 0 && lp + 1 < (int)n->u64_offs.size() && n->u64_offs[lp + 1] > n->u64_offs[lp]) n->u64_vals[n->u64_offs[lp]] = 0;
+        if (lf >= 0 && lf + 1 < (int)n->f_offs.size() && n->f_offs[lf + 1] > n->f_offs[lf]) n->f_vals[n->f_offs[lf]] = 0.f;
+      }
+      out.push_back(n);
+    }
+  }
+  records_.swap(out);
+  if (!dropped.empty()) pool_.put(dropped);
+  int64_t feas = 0;
+  for (const SlotRecord* r : records_) feas += (int64_t)r->u64_vals.size();
+  total_feasigns_ = feas;
+  if (collect_keys) {      // the sampled node ids are embedding keys of this pass too
+    unique_keys_.insert(unique_keys_.end(), ids, ids + total);
+    radix_sort_u64(unique_keys_);
+    unique_keys_.erase(std::unique(unique_keys_.begin(), unique_keys_.end()), unique_keys_.end());
+  }
+  return 0;
+}
+
 // Merge the records that share an instance id into one (reference MultiSlotDataset::MergeByInsId,
 // data_set.cc:1387-1581): groups whose size differs from merge_size (> 0) are dropped; a sparse
 // slot may carry values in at most one record of a group (else the group is dropped as

@@ -148,6 +148,11 @@ class Dataset {
   int64_t merge_by_ins_id(int merge_size);   // merge records sharing an ins_id; returns dropped instances
   int slots_shuffle(const std::vector<int>& slot_idx, uint64_t seed, bool inverse = false);  // AUC runner: permute slots across records
   int prepare_train(int nworkers, bool shuffle, uint64_t seed, int64_t min_batches);
+  // TDM sampling support (reference LayerWiseSampler::sample_from_dataset, index_sampler.cc:75-128): read the
+  // first feasign of one sparse slot of every record, then replace record i by counts[i] copies whose feasign
+  // in that slot is ids[k]; copies flagged neg[k] get the first value of label_slot (sparse or float) zeroed.
+  int slot_first_values(int slot, uint64_t* out, uint8_t* has) const;
+  int expand_records(int slot, int label_slot, const int64_t* counts, const uint64_t* ids, const uint8_t* neg);
   int64_t num_records() const { return arena_only_ ? arena_n_ : (int64_t)records_.size(); }
   // Pass file: the compact arena (and the pass's unique keys) written as-is and mapped back with no
   // per-record decode — a pre-processed pass loads at page-cache speed (role: the reference's

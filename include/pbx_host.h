@@ -34,6 +34,11 @@ int64_t pbh_dataset_merge_by_ins_id(void* ds, int merge_size);
 int pbh_dataset_slots_shuffle(void* ds, const int* slots, int n, uint64_t seed);
 /* undoes pbh_dataset_slots_shuffle called with the same slots and seed */
 int pbh_dataset_slots_shuffle_back(void* ds, const int* slots, int n, uint64_t seed);
+/* TDM sampling: first feasign of a sparse slot per record (has[i] = 0 when the slot is empty), and the rewrite of
+ * the record list: record i becomes counts[i] copies with that feasign replaced by ids[k]; copies with neg[k] get
+ * the first value of label_slot (-1: none) zeroed; records with an empty slot or count 0 are dropped */
+int pbh_dataset_slot_first_values(void* ds, int slot, uint64_t* out, uint8_t* has);
+int pbh_dataset_expand_records(void* ds, int slot, int label_slot, const int64_t* counts, const uint64_t* ids, const uint8_t* neg);
 int pbh_dataset_prepare_train(void* ds, int nworkers, int shuffle, uint64_t seed, int64_t min_batches);
 int64_t pbh_dataset_num_records(void* ds);
 int64_t pbh_dataset_num_batches(void* ds, int worker);

@@ -597,6 +597,30 @@ class InMemoryDataset(DatasetBase):
     def unique_keys(self) -> np.ndarray:
         return self._native.unique_keys()
 
+    def tdm_sample(self, tree_name: str, tree_path: str, tdm_layer_counts, start_sample_layer: int = 1,
+                   with_hierachy: bool = False, seed: int = 0, id_slot=0, label_slot=None) -> int:
+        """Layer-wise TDM sampling of the loaded records (data_set.cc:694-768, index_sampler.cc:75-128): a record
+        whose ``id_slot`` holds item i becomes one positive record per node on i's path in the tree (the slot's
+        feasign replaced by the node id) plus that layer's negatives (a random node of the layer, label zeroed).
+        ``id_slot`` / ``label_slot``: slot index or name; the label defaults to the slot after ``id_slot``.
+        Records without a value in ``id_slot`` are dropped.  Returns the new record count."""
+        from .index_dataset import IndexSampler, IndexWrapper
+        names = [s.name for s in self.all_slots]
+        idx = names.index(id_slot) if isinstance(id_slot, str) else int(id_slot)
+        if label_slot is None:
+            lab = idx + 1 if idx + 1 < len(names) else -1
+        else:
+            lab = names.index(label_slot) if isinstance(label_slot, str) else int(label_slot)
+        IndexWrapper().insert_tree_index(tree_name, tree_path)
+        sampler = IndexSampler("by_layerwise", tree_name)
+        sampler.init_layerwise_conf(list(tdm_layer_counts), start_sample_layer, seed)
+        targets, has = self._native.slot_first_values(idx)
+        counts = np.where(has, sampler.layer_counts_sum, 0).astype(np.int64)
+        codes, labels = sampler.sample_codes(targets[has])
+        ids = sampler.tree.node_ids_of(codes.reshape(-1))
+        self._native.expand_records(idx, lab, counts, ids, (labels.reshape(-1) == 0))
+        return self._native.num_records()
+
     def _generate_local_tables_unlock(self, table_id=0, fea_dim=0, read_thread_num=1, consume_thread_num=1,
                                       shard_num=1) -> int:
         """The reference builds per-shard key tables from the loaded records for the heterogeneous PS
@@ -857,6 +881,42 @@ class BoxPSDataset(InMemoryDataset):
     def read_ins_into_memory(self):
         """``BoxHelper::ReadData2Memory``: BeginFeedPass -> LoadIntoMemory -> EndFeedPass."""
         self.load_into_memory()
+
+
+class BoxPS:
+    """``core.BoxPS(dataset)`` — the reference's ``BoxHelper`` (pybind/box_helper_py.cc:38-67, box_wrapper.h:1043-1295):
+    the pass lifecycle calls for one dataset.  ``BoxPSDataset`` carries the same methods itself; this is the object
+    scripts that construct the helper directly expect."""
+
+    def __init__(self, dataset: "BoxPSDataset"):
+        if not isinstance(dataset, BoxPSDataset):
+            raise TypeError("BoxPS needs a BoxPSDataset / PadBoxSlotDataset")
+        self.dataset = dataset
+
+    def set_date(self, year, month=None, day=None):
+        """``set_date(2021, 5, 17)`` as the helper takes it, or one ``"20210517"`` string."""
+        self.dataset.set_date(f"{int(year):04d}{int(month):02d}{int(day):02d}" if month is not None else str(year))
+
+    def begin_pass(self):
+        self.dataset.begin_pass()
+
+    def end_pass(self, need_save_delta: bool = False):
+        self.dataset.end_pass(need_save_delta)
+
+    def load_into_memory(self):
+        self.dataset.load_into_memory()
+
+    def preload_into_memory(self):
+        self.dataset.preload_into_memory()
+
+    def wait_feed_pass_done(self):
+        self.dataset.wait_feed_pass_done()
+
+    def read_ins_into_memory(self):
+        self.dataset.read_ins_into_memory()
+
+    def slots_shuffle(self, slots):
+        self.dataset.slots_shuffle(list(slots))
 
 
 class PadBoxSlotDataset(BoxPSDataset):

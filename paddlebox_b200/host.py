@@ -382,6 +382,25 @@ class NativeDataset:
         n = len(slot_indices)
         N.hcheck(N.host().pbh_dataset_slots_shuffle_back(self._h, (C.c_int * n)(*slot_indices), n, C.c_uint64(seed)))
 
+    def slot_first_values(self, slot_index: int):
+        """``(values uint64 [n_records], has bool [n_records])``: the first feasign of one sparse slot per record."""
+        n = self.num_records()
+        out, has = np.zeros(n, dtype=np.uint64), np.zeros(n, dtype=np.uint8)
+        N.hcheck(N.host().pbh_dataset_slot_first_values(self._h, int(slot_index), _u64p(out),
+                                                        has.ctypes.data_as(C.POINTER(C.c_uint8))))
+        return out, has.astype(bool)
+
+    def expand_records(self, slot_index: int, label_slot_index: int, counts, ids, neg) -> None:
+        """Record i -> ``counts[i]`` copies with the slot's first feasign replaced by the next ``ids``; copies
+        flagged in ``neg`` get the label slot's first value zeroed (TDM layer-wise sampling)."""
+        counts = np.ascontiguousarray(counts, dtype=np.int64)
+        ids = np.ascontiguousarray(ids, dtype=np.uint64)
+        neg = np.ascontiguousarray(neg, dtype=np.uint8)
+        assert counts.size == self.num_records() and ids.size == int(counts.sum()) == neg.size
+        N.hcheck(N.host().pbh_dataset_expand_records(self._h, int(slot_index), int(label_slot_index),
+                                                     counts.ctypes.data_as(C.POINTER(C.c_int64)), _u64p(ids),
+                                                     neg.ctypes.data_as(C.POINTER(C.c_uint8))))
+
     def prepare_train(self, nworkers: int, shuffle: bool = True, seed: int = 0, min_batches: int = 0):
         N.hcheck(N.host().pbh_dataset_prepare_train(self._h, nworkers, int(shuffle), C.c_uint64(seed),
                                                     C.c_int64(min_batches)))

@@ -337,3 +337,27 @@ def test_dataset_generator_check_and_local_tables(tmp_path):
         ds._check_use_var_with_data_generator(use[:1], Gen(), str(f))
     ds.set_use_var(use)
     assert ds._desc() == ds.desc()
+
+
+def test_boxps_helper_object_drives_the_pass_lifecycle(tmp_path):
+    import torch
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    from paddlebox_b200.dataset import BoxPS, DatasetFactory
+    from tests.util_data import slot_vars, write_files
+    box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"))
+    box.initialize_gpu_and_load_model({})
+    ds = DatasetFactory().create_dataset("PadBoxSlotDataset")
+    ds.set_use_var(slot_vars(3, 1))
+    ds.set_batch_size(8)
+    ds.set_filelist(write_files(str(tmp_path), n_files=1, lines_per_file=40, n_sparse=3, n_dense=1, key_space=30, seed=1))
+    helper = BoxPS(ds)
+    helper.set_date(2024, 1, 2)
+    assert ds._date == "20240102"
+    helper.preload_into_memory()
+    helper.wait_feed_pass_done()
+    helper.begin_pass()
+    assert ds.get_memory_data_size() == 40 and box.host_table.size() > 0
+    helper.end_pass(False)
+    with pytest.raises(TypeError):
+        BoxPS(DatasetFactory().create_dataset("QueueDataset"))
+    BoxWrapper.reset_instance()
