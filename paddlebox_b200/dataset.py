@@ -60,6 +60,16 @@ def dense_slot(name: str, dim: int = 1) -> SlotVar:
     return SlotVar(name, "float32", 0, (-1, dim))
 
 
+def _is_id_list_file(path: str) -> bool:
+    """A text file of item ids (digits and white space) rather than a binary tree-index file."""
+    try:
+        with open(path, "rb") as f:
+            head = f.read(256)
+    except OSError:
+        return False
+    return bool(head) and all(c in b"0123456789 \t\r\n" for c in head)
+
+
 class DatasetBase:
     def __init__(self):
         self._native = NativeDataset()
@@ -208,6 +218,32 @@ class DatasetBase:
 
     def _desc(self) -> str:
         return self.desc()
+
+    # getters of the native dataset object (pybind/data_set_py.cc) --------------------------------------------------
+    def get_data_feed_desc(self) -> str:
+        return self.desc()
+
+    def get_filelist(self) -> list:
+        return list(self.filelist)
+
+    def get_thread_num(self) -> int:
+        return int(self.thread_num)
+
+    def get_trainer_num(self) -> int:
+        return int(self.trainer_num)
+
+    def get_hdfs_config(self) -> tuple:
+        return (self.fs_name, self.fs_ugi)
+
+    def get_download_cmd(self) -> str:
+        return self.download_cmd
+
+    def get_fleet_send_batch_size(self) -> int:
+        return int(getattr(self, "fleet_send_batch_size", 1024))
+
+    def register_client2client_msg_handler(self) -> None:
+        """The reference hooks the shuffle receiver into the PS client here; the shuffle transport of this
+        framework (parallel/shuffle.py) sets itself up when ``global_shuffle`` runs."""
 
     def set_data_feed_desc(self, desc: str):
         """Configure from the protobuf TEXT form of a ``DataFeedDesc`` (data_feed.proto:18-57; what ``desc()``
@@ -426,9 +462,9 @@ class InMemoryDataset(DatasetBase):
         """Batches come from ``graph.GraphDataGenerator`` walks instead of files."""
         self.gpu_graph_mode = bool(v)
 
-    def tdm_sample(self, tree_name: str, tree_path, tdm_layer_counts, start_sample_layer: int = 1,
-                   with_hierarchy: bool = False, seed: int = 0, id_slot: int = 0, branch: int = 2):
-        """Bind a TDM item tree to the dataset (``Dataset.tdm_sample``).  ``tree_path``: a file with one
+    def _tdm_tensor_sampler(self, tree_name: str, tree_path, tdm_layer_counts, start_sample_layer: int = 1,
+                            with_hierarchy: bool = False, seed: int = 0, id_slot: int = 0, branch: int = 2):
+        """Bind a TDM item tree to the dataset (``tdm_sample`` with a list of item ids instead of a tree file).  ``tree_path``: a file with one
         item id per line (leaf order) or a sequence of item ids.  Returns ``sampler(item_ids) ->
         (nodes, labels, mask)`` (``ops.tdm.tdm_sample`` with ``tdm_layer_counts`` negatives per layer),
         to be applied to the ids of slot ``id_slot`` in the model's forward."""
@@ -603,8 +639,13 @@ class InMemoryDataset(DatasetBase):
         whose ``id_slot`` holds item i becomes one positive record per node on i's path in the tree (the slot's
         feasign replaced by the node id) plus that layer's negatives (a random node of the layer, label zeroed).
         ``id_slot`` / ``label_slot``: slot index or name; the label defaults to the slot after ``id_slot``.
-        Records without a value in ``id_slot`` are dropped.  Returns the new record count."""
+        Records without a value in ``id_slot`` are dropped.  Returns the new record count.  (``tree_path`` given as
+        a sequence of item ids, or a text file of them, binds the tensor-side sampler of the base class instead.)"""
         from .index_dataset import IndexSampler, IndexWrapper
+        if not isinstance(tree_path, str) or _is_id_list_file(tree_path):
+            # a plain list of item ids (no tree file): the tensor-side sampler to call in the model's forward
+            return self._tdm_tensor_sampler(tree_name, tree_path, tdm_layer_counts, start_sample_layer, with_hierachy,
+                                            seed, id_slot if isinstance(id_slot, int) else 0)
         names = [s.name for s in self.all_slots]
         idx = names.index(id_slot) if isinstance(id_slot, str) else int(id_slot)
         if label_slot is None:

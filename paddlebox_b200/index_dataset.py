@@ -100,7 +100,10 @@ class IndexNode:
     @classmethod
     def _decode(cls, buf: bytes) -> "IndexNode":
         n = cls()
+        want = {1: 0, 2: 0, 3: 5, 4: 2}
         for num, wt, v in _fields(buf):
+            if num in want and wt != want[num] or (wt == 5 and len(v) != 4):
+                raise ValueError(f"tree index: field {num} of a node has wire type {wt}")
             if num == 1:
                 n._id = v
             elif num == 2:
@@ -128,6 +131,12 @@ class _Tree:
     """The loaded index (``TreeIndex`` of index_wrapper.h:33-90)."""
 
     def __init__(self, path: str):
+        try:
+            self._load(path)
+        except (IndexError, struct.error, UnicodeDecodeError, OverflowError) as e:
+            raise ValueError(f"tree index {path}: damaged file ({type(e).__name__}: {e})") from None
+
+    def _load(self, path: str) -> None:
         codes, nodes = [], []
         self._height = self._branch = 0
         with open(path, "rb") as f:
@@ -142,6 +151,8 @@ class _Tree:
                 raise ValueError(f"tree index {path}: record of {n} bytes runs past the end of the file")
             key = value = b""
             for num, wt, v in _fields(buf[pos:pos + n]):
+                if num in (1, 2) and wt != 2:
+                    raise ValueError(f"tree index {path}: key / value field with wire type {wt}")
                 if num == 1:
                     key = v
                 elif num == 2:
@@ -149,6 +160,8 @@ class _Tree:
             pos += n
             if key == b".tree_meta":
                 for num, wt, v in _fields(value):
+                    if wt != 0:
+                        raise ValueError(f"tree index {path}: .tree_meta field {num} has wire type {wt}")
                     if num == 1:
                         self._height = v
                     elif num == 2:
@@ -156,8 +169,10 @@ class _Tree:
             else:
                 codes.append(int(key))
                 nodes.append(IndexNode._decode(value))
-        if self._branch < 2 or self._height < 1:
+        if not 2 <= self._branch <= 1 << 16 or not 1 <= self._height <= 64:
             raise ValueError(f"tree index {path}: no valid .tree_meta (height {self._height}, branch {self._branch})")
+        if codes and (min(codes) < 0 or max(codes) >= 1 << 63):
+            raise ValueError(f"tree index {path}: node code out of range")
         order = np.argsort(np.asarray(codes, dtype=np.uint64), kind="stable")
         self._codes = np.asarray(codes, dtype=np.uint64)[order]
         self._nodes = [nodes[i] for i in order]

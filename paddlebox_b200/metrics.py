@@ -336,3 +336,69 @@ def create_metric(method: str, **kw) -> MetricMsg:
         if kw.get(opt, None) == "":
             kw.pop(opt)
     return cls(**kw)
+
+
+class Metric:
+    """``core.Metric()`` — the metric registry of the PSLIB / PSGPU path (fleet/metrics.h:640-820,
+    pybind/metrics_py.cc): the same calculators as ``BoxWrapper.init_metric``, for jobs that run without a
+    ``BoxWrapper``.  One instance per process; the trainers feed it next to the wrapper's metrics
+    (``add_metric_data``), results are reduced over the ``torch.distributed`` world."""
+    _instance = None
+
+    def __new__(cls):
+        if cls._instance is None:
+            cls._instance = super().__new__(cls)
+            cls._instance._metrics = {}
+            cls._instance._phase = 1
+        return cls._instance
+
+    @classmethod
+    def get_instance(cls):
+        return cls._instance
+
+    @classmethod
+    def reset_instance(cls) -> None:
+        cls._instance = None
+
+    def init_metric(self, method: str, name: str, label_varname: str = "label", pred_varname: str = "pred",
+                    cmatch_rank_varname: str = "", mask_varname: str = "", uid_varname: str = "", metric_phase: int = 1,
+                    cmatch_rank_group: str = "", ignore_rank: bool = False, bucket_size: int = 1000000) -> None:
+        kw = dict(name=name, label_varname=label_varname, pred_varname=pred_varname, cmatch_rank_varname=cmatch_rank_varname,
+                  mask_varname=mask_varname, metric_phase=metric_phase, cmatch_rank_group=cmatch_rank_group,
+                  ignore_rank=ignore_rank, bucket_size=bucket_size)
+        if uid_varname:
+            kw["uid_varname"] = uid_varname
+        self._metrics[name] = create_metric(method, **kw)
+
+    def flip_phase(self) -> None:
+        self._phase = (self._phase + 1) % 2
+
+    def phase(self) -> int:
+        return self._phase
+
+    def get_metric_name_list(self, metric_phase: int = -1) -> list:
+        return [n for n, m in self._metrics.items() if metric_phase < 0 or m.metric_phase == metric_phase]
+
+    def add_metric_data(self, tensors: dict) -> None:
+        for m in self._metrics.values():
+            if m.metric_phase == self._phase:
+                m.add_data(tensors)
+
+    @staticmethod
+    def _group():
+        import torch.distributed as dist
+        return dist.group.WORLD if dist.is_available() and dist.is_initialized() and dist.get_world_size() > 1 else None
+
+    def _get(self, name: str):
+        if name not in self._metrics:
+            raise ValueError("The metric name you provided is not registered.")
+        return self._metrics[name]
+
+    def get_metric_msg(self, name: str) -> list:
+        """[auc, bucket_error, mae, rmse, actual_ctr, predicted_ctr, copc, size]; resets the metric."""
+        return self._get(name).get_metric_msg(self._group())
+
+    def get_wuauc_metric_msg(self, name: str) -> list:
+        """[user_cnt, size, sum of user AUCs, sum of (user AUC * instances), uauc, wuauc]; resets the metric."""
+        uauc, wuauc, users, size = self._get(name).get_metric_msg(self._group())
+        return [users, size, uauc * users, wuauc * size, uauc, wuauc]

@@ -15,6 +15,7 @@ from dataclasses import dataclass, field
 import torch
 
 from .box_wrapper import BoxWrapper
+from . import metrics as _metrics
 from .flags import FLAGS
 from .parallel.dense import DenseOptimizer, DenseParamStore, DenseSync
 from .utils.nan_inf import check_batch_nan_inf
@@ -312,6 +313,8 @@ class CTRTrainer:
         with torch.no_grad():
             loss, outs = self.model(batch)
         self.box.add_metric_data(outs)
+        if _metrics.Metric._instance is not None:
+            _metrics.Metric._instance.add_metric_data(outs)
         return loss, outs
 
     def _after_batch(self, batch, loss, outs):
@@ -324,6 +327,8 @@ class CTRTrainer:
                                                   if torch.is_tensor(v) and (not names or k in names)}},
                                 self.cfg.dump_fields_path or None, tag=f"rank{self.rank}_step{self.steps}")
         self.box.add_metric_data(outs)           # AddAucMonitor
+        if _metrics.Metric._instance is not None:
+            _metrics.Metric._instance.add_metric_data(outs)
         if self.dumper is not None and self.cfg.dump_fields and batch.ins_ids is not None:
             self.dumper.dump_batch(batch.ins_ids, outs)
 

@@ -361,3 +361,45 @@ def test_boxps_helper_object_drives_the_pass_lifecycle(tmp_path):
     with pytest.raises(TypeError):
         BoxPS(DatasetFactory().create_dataset("QueueDataset"))
     BoxWrapper.reset_instance()
+
+
+def test_core_metric_registry_and_dataset_getters(tmp_path):
+    import torch
+    from paddlebox_b200.box_wrapper import BoxWrapper
+    from paddlebox_b200.dataset import DatasetFactory
+    from paddlebox_b200.metrics import Metric
+    from paddlebox_b200.models.ctr import CtrDnn
+    from paddlebox_b200.trainer import CTRTrainer, TrainerConfig
+    from tests.util_data import slot_vars, write_files
+    Metric.reset_instance()
+    m = Metric()
+    assert Metric() is m and Metric.get_instance() is m
+    m.init_metric("AucCalculator", "auc", "label", "pred", "", "", "", 1, "", False, 100000)
+    m.init_metric("WuAucCalculator", "wu", "label", "pred", "", "", "uid", 0, "", False)
+    assert m.get_metric_name_list(1) == ["auc"] and m.get_metric_name_list(-1) == ["auc", "wu"]
+    with pytest.raises(ValueError):
+        m.get_metric_msg("nosuch")
+    box = BoxWrapper.set_instance(embedx_dim=4, device=torch.device("cpu"))
+    box.initialize_gpu_and_load_model({})
+    ds = DatasetFactory().create_dataset("PadBoxSlotDataset")
+    ds.set_use_var(slot_vars(3, 1))
+    ds.set_batch_size(16)
+    ds.set_thread(2)
+    files = write_files(str(tmp_path), n_files=1, lines_per_file=64, n_sparse=3, n_dense=1, key_space=30, seed=1)
+    ds.set_filelist(files)
+    ds.set_hdfs_config("afs://x", "u,p")
+    assert ds.get_filelist() == files and ds.get_thread_num() == 2 and ds.get_trainer_num() == 1
+    assert ds.get_hdfs_config() == ("afs://x", "u,p") and ds.get_download_cmd() == ds.download_cmd
+    assert ds.get_data_feed_desc() == ds.desc() and ds.get_fleet_send_batch_size() > 0
+    ds.register_client2client_msg_handler()
+    ds.load_into_memory()
+    ds.begin_pass()
+    CTRTrainer(CtrDnn(num_slots=3, embedx_dim=4, dense_dim=1, hidden=(4,)), box, TrainerConfig()).train_from_dataset(ds)
+    ds.end_pass(False)
+    msg = m.get_metric_msg("auc")                               # the trainer fed the registry as well
+    assert len(msg) == 8 and msg[7] == 64 and 0.0 <= msg[0] <= 1.0
+    assert m.get_metric_msg("auc")[7] == 0                       # reading resets
+    m.flip_phase()
+    assert m.phase() == 0
+    Metric.reset_instance()
+    BoxWrapper.reset_instance()

@@ -129,3 +129,27 @@ def test_dataset_tdm_sample_expands_records(tmp_path):
     assert sum(100 <= v <= 107 for v in pos_items) == 20 and sum(v in (1001, 1002) for v in pos_items) == 20
     users, _ = ds._native.slot_first_values(0)
     assert sorted(set(users.tolist())) == [900 + i for i in range(20)]       # other slots ride along unchanged
+
+
+def test_damaged_tree_files_are_refused_not_crashed_on(tmp_path):
+    _write_tree(tmp_path / "tree.pb")
+    good = (tmp_path / "tree.pb").read_bytes()
+    rng = np.random.RandomState(0)
+    outcomes = {"ok": 0, "refused": 0}
+    for trial in range(300):
+        buf = bytearray(good)
+        if trial % 2:
+            del buf[rng.randint(1, len(buf)):]                                 # truncated
+        else:
+            for _ in range(rng.randint(1, 4)):
+                buf[rng.randint(0, len(buf))] ^= 1 << rng.randint(0, 8)        # flipped bits
+        p = tmp_path / "damaged.pb"
+        p.write_bytes(bytes(buf))
+        IndexWrapper().clear_tree()
+        try:
+            t = TreeIndex("d", str(p))
+            t.get_layer_codes(1), t.get_all_leafs(), t.get_ancestor_codes([100, 103], 1), t.get_children_codes(0, 2)
+            outcomes["ok"] += 1
+        except ValueError:
+            outcomes["refused"] += 1
+    assert outcomes["ok"] + outcomes["refused"] == 300 and outcomes["refused"] > 0
