@@ -134,6 +134,8 @@ class _Util:
 
 util = _Util()
 
+from .distributed_strategy import DistributedStrategy  # noqa: E402,F401  ``fleet.DistributedStrategy()``
+
 from . import fleet_metrics as metrics  # noqa: E402,F401  ``fleet.metrics.auc(stat_pos, stat_neg)`` ...
 
 
@@ -269,6 +271,10 @@ def distributed_optimizer(optimizer, strategy=None):
     ``sparse_delete_threshold`` ...) configures the wrapper's sparse optimizer (if the wrapper is initialised
     already) and the thresholds ``shrink_sparse_table`` / ``save_persistables`` use by default."""
     from .optimizer import BoxPSOptimizer
+    from .distributed_strategy import DistributedStrategy as _DS
+    ds = strategy if isinstance(strategy, _DS) else None
+    if ds is not None:
+        strategy = ds.sparse_strategy()
     if strategy:
         from .fleet_desc import sparse_config_from_strategy
         conf, kind, _, policy = sparse_config_from_strategy(dict(strategy))
@@ -284,7 +290,14 @@ def distributed_optimizer(optimizer, strategy=None):
             if getattr(box, "table", None) is not None:
                 box.table.set_config(cfg)
     global _last_optimizer
-    _last_optimizer = optimizer if isinstance(optimizer, BoxPSOptimizer) else BoxPSOptimizer(optimizer)
+    if isinstance(optimizer, BoxPSOptimizer):
+        _last_optimizer = optimizer
+    elif ds is not None:
+        mode, k, is_async = ds.dense_mode()
+        _last_optimizer = BoxPSOptimizer(optimizer, sync_steps=k, sync_dense_mode=mode, async_mode=is_async)
+    else:
+        _last_optimizer = BoxPSOptimizer(optimizer)
+    _last_optimizer._strategy = ds
     return _last_optimizer
 
 

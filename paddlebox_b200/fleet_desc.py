@@ -189,6 +189,18 @@ def sparse_config_from_fleet_desc(text: str | dict, table: int = 0):
     return conf, optimizer, extra
 
 
+# keys a job's strategy may carry for the sparse table (pslib/node.py, distributed_strategy.py ``fleet_desc_configs``);
+# each may also be prefixed ``embed_`` / ``embedx_`` for the two halves of a unit accessor
+STRATEGY_KEYS = frozenset((
+    "sparse_table_class", "sparse_compress_in_save", "sparse_shard_num", "sparse_accessor_class", "sparse_learning_rate",
+    "sparse_initial_g2sum", "sparse_initial_range", "sparse_weight_bounds", "sparse_fea_dim", "sparse_embedx_dim",
+    "sparse_embedx_threshold", "sparse_nonclk_coeff", "sparse_click_coeff", "sparse_base_threshold", "sparse_delta_threshold",
+    "sparse_delta_keep_days", "sparse_delete_after_unseen_days", "sparse_show_click_decay_rate", "sparse_delete_threshold",
+    "sparse_converter", "sparse_deconverter", "sparse_enable_cache", "sparse_cache_rate", "sparse_cache_file_num",
+    "sparse_beta1_decay_rate", "sparse_beta2_decay_rate", "sparse_ada_epsilon", "sparse_optimizer",
+    "sparse_ssd_unseenday_threshold", "feature_learning_rate", "nodeid_slot"))
+
+
 def sparse_config_from_strategy(strategy: dict, prefix: str = ""):
     """The ``strategy`` dict a pslib job gives ``fleet.distributed_optimizer(optimizer, strategy)`` (the reference
     turns it into the fleet description, pslib/node.py:80-330) -> ``(SparseOptConfig keywords, optimizer kind,

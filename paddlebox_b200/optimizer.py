@@ -72,6 +72,11 @@ class BoxPSOptimizer:
         cfg = TrainerConfig(dense_lr=self._optimizer.lr, dense_optimizer=self._optimizer.kind,
                             sync_dense_mode=self._mode, sync_weight_step=max(1, self._sync_steps),
                             async_mode=self._async, dump_thread_num=self._dump_thread_num)
+        if getattr(self, "_strategy", None) is not None:          # fleet.DistributedStrategy: dump fields etc.
+            td = self._strategy.trainer_desc_configs
+            cfg.dump_fields_path = td["dump_fields_path"] or cfg.dump_fields_path
+            cfg.dump_fields = list(td["dump_fields"]) or cfg.dump_fields
+            cfg.dump_param = list(td["dump_param"]) or cfg.dump_param
         model._pipeline_opt = cfg
         model._param_need_sync = [n for n, p in model.named_parameters() if p.requires_grad]
         return cfg
