@@ -17,6 +17,7 @@ _cluster: Cluster | None = None
 
 
 _role_maker = None
+_init_strategy = None
 
 
 def init(role_maker=None, is_collective: bool = True, strategy=None, backend: str | None = None) -> None:
@@ -25,10 +26,14 @@ def init(role_maker=None, is_collective: bool = True, strategy=None, backend: st
     (``role_maker.py``: ``GeneralRoleMaker``, ``PaddleCloudRoleMaker`` ...): rank, world size and the rendezvous
     address come from the Paddle launcher's variables it reads (``PADDLE_TRAINER_ID``, ``PADDLE_TRAINER_ENDPOINTS``,
     ``TRAINING_ROLE``); a process launched as a parameter server joins nothing (there are no server processes)."""
-    global _cluster, _role_maker
+    global _cluster, _role_maker, _init_strategy
     import datetime
     import torch.distributed as dist
     _role_maker = role_maker
+    _init_strategy = strategy                  # fleet 2.0: the strategy may be given here instead of to the optimizer
+    backend = backend or os.environ.get("PADDLE_DISTRI_BACKEND") or None
+    if backend == "auto":
+        backend = None
     rank, world, addr, port, timeout = None, None, None, None, None
     if role_maker is not None:
         role_maker.generate_role()
@@ -272,6 +277,8 @@ def distributed_optimizer(optimizer, strategy=None):
     already) and the thresholds ``shrink_sparse_table`` / ``save_persistables`` use by default."""
     from .optimizer import BoxPSOptimizer
     from .distributed_strategy import DistributedStrategy as _DS
+    if strategy is None:
+        strategy = _init_strategy
     ds = strategy if isinstance(strategy, _DS) else None
     if ds is not None:
         strategy = ds.sparse_strategy()

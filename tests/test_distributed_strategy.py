@@ -67,3 +67,14 @@ def test_distributed_optimizer_applies_a_strategy_object():
     assert s3.sparse_strategy()["sparse_optimizer"] == "adam"
     fleet.table_policy.clear()
     BoxWrapper.reset_instance()
+
+
+def test_strategy_given_to_fleet_init_is_used_by_the_optimizer():
+    s = fleet.DistributedStrategy()
+    s.a_sync = False
+    fleet.init(is_collective=True, strategy=s)
+    try:
+        opt = fleet.distributed_optimizer(Adam(0.02))
+        assert opt._strategy is s and opt.minimize(torch.nn.Linear(2, 1)).sync_dense_mode == "allreduce"
+    finally:
+        fleet._init_strategy = None
