@@ -25,6 +25,7 @@ from .ops.sequence import (bpr_loss, hash, log_loss, margin_rank_loss, match_mat
                            sequence_first_step, sequence_last_step, sequence_mask, sequence_pad, sequence_pool,
                            sequence_reshape, sequence_reverse, sequence_scatter, sequence_slice, sequence_softmax,
                            sequence_topk_avg_pooling, sequence_unpad, teacher_student_sigmoid_loss)
+from .metrics import Auc, auc  # noqa: F401
 from .ops.tdm import TDMTree, tdm_child, tdm_sampler  # noqa: F401
 from .ps_gpu import pull_gpups_sparse  # noqa: F401
 

@@ -402,3 +402,63 @@ class Metric:
         """[user_cnt, size, sum of user AUCs, sum of (user AUC * instances), uauc, wuauc]; resets the metric."""
         uauc, wuauc, users, size = self._get(name).get_metric_msg(self._group())
         return [users, size, uauc * users, wuauc * size, uauc, wuauc]
+
+
+class Auc:
+    """``fluid.layers.auc(input, label, curve='ROC', num_thresholds=2**12 - 1, topk=1, slide_steps=1)`` as an object
+    (layers/metric_op.py:100-240, operators/metrics/auc_op.h): bucket counts of positives / negatives by
+    ``floor(p * num_thresholds)``, accumulated over the calls.  ``__call__`` returns what the layer returns —
+    ``(auc over everything seen, auc over the last slide_steps batches, [batch_stat_pos, batch_stat_neg, stat_pos,
+    stat_neg])`` — and the last two are the statistics ``fleet.metrics.auc(stat_pos, stat_neg)`` reduces over the
+    workers.  ``slide_steps`` 0 makes the batch AUC cover everything as well."""
+
+    def __init__(self, curve: str = "ROC", num_thresholds: int = 2 ** 12 - 1, topk: int = 1, slide_steps: int = 1):
+        if curve != "ROC":
+            raise ValueError("only the ROC curve is computed from bucket statistics")
+        self.num_thresholds, self.slide_steps = int(num_thresholds), int(slide_steps)
+        n = self.num_thresholds + 1
+        self.stat_pos = torch.zeros(1, n, dtype=torch.int64)
+        self.stat_neg = torch.zeros(1, n, dtype=torch.int64)
+        self._window: list = []
+
+    @staticmethod
+    def area(stat_pos: torch.Tensor, stat_neg: torch.Tensor) -> float:
+        pos_b, neg_b = stat_pos.reshape(-1).flip(0).double(), stat_neg.reshape(-1).flip(0).double()
+        pos_run = pos_b.cumsum(0)
+        area = float((neg_b * (2 * pos_run - pos_b) / 2).sum())
+        pos, neg = float(pos_run[-1]), float(neg_b.sum())
+        return 0.5 if pos * neg == 0 else area / (pos * neg)
+
+    def __call__(self, input: torch.Tensor, label: torch.Tensor):
+        p = input.detach()
+        p = (p[:, 1] if p.dim() == 2 and p.shape[1] == 2 else p.reshape(-1)).float().cpu()
+        y = label.detach().reshape(-1).cpu() > 0
+        b = (p * self.num_thresholds).long().clamp_(0, self.num_thresholds)
+        n = self.num_thresholds + 1
+        bp, bn = torch.bincount(b[y], minlength=n).view(1, n), torch.bincount(b[~y], minlength=n).view(1, n)
+        self.stat_pos += bp
+        self.stat_neg += bn
+        if self.slide_steps > 0:
+            self._window.append((bp, bn))
+            del self._window[:-self.slide_steps]
+            wp, wn = sum(w[0] for w in self._window), sum(w[1] for w in self._window)
+        else:
+            wp, wn = self.stat_pos, self.stat_neg
+        return self.area(self.stat_pos, self.stat_neg), self.area(wp, wn), [wp, wn, self.stat_pos, self.stat_neg]
+
+    def reset(self) -> None:
+        self.stat_pos.zero_()
+        self.stat_neg.zero_()
+        self._window.clear()
+
+
+_AUC_LAYERS: dict = {}
+
+
+def auc(input: torch.Tensor, label: torch.Tensor, curve: str = "ROC", num_thresholds: int = 2 ** 12 - 1, topk: int = 1,
+        slide_steps: int = 1, name: str = "auc"):
+    """Function form of :class:`Auc`; the accumulated statistics live under ``name`` (one per metric of the model)."""
+    key = (name, num_thresholds, slide_steps)
+    if key not in _AUC_LAYERS:
+        _AUC_LAYERS[key] = Auc(curve, num_thresholds, topk, slide_steps)
+    return _AUC_LAYERS[key](input, label)

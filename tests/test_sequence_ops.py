@@ -208,3 +208,34 @@ def test_slot_lod_feeds_the_ragged_ops():
     emb = torch.arange(9.0).view(9, 1)
     (b0, e0), (b1, e1) = b.slot_ranges()
     assert S.sequence_pool(emb[b1:e1], b.slot_lod(1), "sum").view(-1).tolist() == [3 + 4 + 5, 6, 7 + 8]
+
+
+def test_auc_layer_statistics_feed_fleet_metrics():
+    from paddlebox_b200 import fleet
+    from paddlebox_b200.host import HostAuc
+    g = torch.Generator().manual_seed(2)
+    layer = L.Auc(num_thresholds=4095, slide_steps=2)
+    preds, labels = [], []
+    for step in range(4):
+        p = torch.rand(500, generator=g)
+        y = (torch.rand(500, generator=g) < p).long()
+        preds.append(p), labels.append(y)
+        total, batch, stats = layer(torch.stack([1 - p, p], 1), y.view(-1, 1))
+    P, Y = torch.cat(preds), torch.cat(labels)
+    # exact AUC by ranks for comparison (bucketing costs a little precision)
+    order = P.argsort()
+    ranks = torch.empty_like(order, dtype=torch.double)
+    ranks[order] = torch.arange(1, P.numel() + 1, dtype=torch.double)
+    npos, nneg = int(Y.sum()), int((1 - Y).sum())
+    exact = (float(ranks[Y == 1].sum()) - npos * (npos + 1) / 2) / (npos * nneg)
+    assert abs(total - exact) < 2e-3
+    last2 = L.Auc.area(*[sum(s) for s in zip(*[(torch.bincount((p * 4095).long()[y == 1], minlength=4096),
+                                                torch.bincount((p * 4095).long()[y == 0], minlength=4096))
+                                               for p, y in zip(preds[-2:], labels[-2:])])])
+    assert abs(batch - last2) < 1e-12 and int(stats[2].sum() + stats[3].sum()) == 2000 and int(stats[0].sum() + stats[1].sum()) == 1000
+    assert abs(fleet.metrics.auc(stats[2], stats[3]) - total) < 1e-12          # one worker: the same number
+    a1 = L.auc(P, Y, name="m1")[0]
+    a2 = L.auc(P, Y, name="m1")[0]                                            # same name: statistics accumulate
+    assert abs(a1 - a2) < 1e-12 and int(L.auc(P, Y, name="m2")[2][2].sum()) == npos
+    layer.reset()
+    assert int(layer.stat_pos.sum()) == 0
