@@ -49,8 +49,8 @@ def test_two_trainers_join_one_world(tmp_path, mode, capfd):
 def test_a_failing_trainer_stops_the_job(tmp_path, capfd):
     import time
     t0 = time.time()
-    rc = L.launch(["--nproc_per_node", "2", "--start_port", str(_free_port()), "--log_dir", str(tmp_path / "log"),
-                   os.path.join(HERE, "launch_worker.py"), "fail"])
+    rc = L.launch(["--nproc_per_node", "2", "--start_port", str(_free_port()), "--master_port", str(_free_port()),
+                   "--log_dir", str(tmp_path / "log"), os.path.join(HERE, "launch_worker.py"), "fail"])
     assert rc == 7 and time.time() - t0 < 45
     assert "exited with code 7" in capfd.readouterr().err
 
@@ -59,13 +59,13 @@ def test_ported_job_script_runs_and_resumes_under_the_launcher(tmp_path, capfd):
     script = os.path.join(os.path.dirname(HERE), "examples", "ported_job.py")
     common = ["--nproc_per_node", "2", "--backend", "gloo", "--log_dir", str(tmp_path / "log")]
     job = ["--cpu", "--out", str(tmp_path / "job"), "--lines", "1500"]
-    rc = L.launch(common + ["--start_port", str(_free_port()), script] + job + ["--epochs", "3"])
+    rc = L.launch(common + ["--start_port", str(_free_port()), "--master_port", str(_free_port()), script] + job + ["--epochs", "3"])
     out = capfd.readouterr().out
     assert rc == 0, out
     assert "epoch 0: 3000 instances" in out and "epochs run: [0, 1, 2]" in out
     auc = float(out.split("epoch 2: 3000 instances, auc ")[1].split()[0])
     assert auc > 0.58, out                                                     # it learns something
-    rc = L.launch(common + ["--start_port", str(_free_port()), script] + job + ["--epochs", "4"])
+    rc = L.launch(common + ["--start_port", str(_free_port()), "--master_port", str(_free_port()), script] + job + ["--epochs", "4"])
     out = capfd.readouterr().out
     assert rc == 0 and "epochs run: [3]" in out and "epoch 0" not in out        # resumed after the saved epochs
     assert float(out.split("epoch 3: 3000 instances, auc ")[1].split()[0]) > 0.58, out   # ... with the trained state
